@@ -1,0 +1,115 @@
+/* ngp_b200 — C ABI of the B200-native (sm_100a) instant-ngp hot path.
+ *
+ * Drop-in boundary for the path SURVEY.md §8 names: hash-grid encoding, fully fused 64-wide MLPs, the NerfNetwork
+ * composition, fused Adam, and the Testbed NeRF / image training step + inference render.  Plain pointers and sizes
+ * only; every `const void* dev_*` / `void* dev_*` argument is a DEVICE pointer, `stream` is a cudaStream_t passed as
+ * void* (NULL = default stream).  All functions return 0 on success, non-zero on failure; ngp_last_error() returns
+ * the message of the last failure on the calling thread (the reference throws std::runtime_error:
+ * CUDA_CHECK_THROW, main.cu:195-209 — the Python binding re-raises it as RuntimeError like pybind11 does).
+ * There is NO CPU fallback: without a CUDA device every compute entry point fails.
+ *
+ * Each entry point cites the reference interface it replaces (paths relative to the reference repo root).
+ */
+#ifndef NGP_B200_H
+#define NGP_B200_H
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NGP_B200_ABI_VERSION 1
+#define NGP_BATCH_GRANULARITY 256u /* tcnn::batch_size_granularity as used at testbed_nerf.cu:2601-2603,3606,3928 */
+
+const char* ngp_last_error(void);
+int ngp_abi_version(void);
+/* number of this library's kernels launched so far on this process (bench.py's gpu_launches) */
+uint64_t ngp_kernel_launch_count(void);
+
+/* activation layouts for encoder outputs / MLP inputs */
+enum { NGP_LAYOUT_ROWMAJOR = 0, /* [n][C] fp16 ("AoS", tcnn::RM with one sample per row) */
+       NGP_LAYOUT_BLK8 = 1      /* 8x8 fp16 core matrices, the tcgen05 no-swizzle operand layout */ };
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Encoding  —  replaces tcnn::create_encoding<T>(n_dims_to_encode, json, alignment) + Encoding::{forward,backward}
+ *   reference call sites: include/neural-graphics-primitives/nerf_network.h:93-95,143-148,201-207,324-333,345-350;
+ *   src/testbed.cu:3961-4005 (config derivation), :4101
+ * ------------------------------------------------------------------------------------------------------------ */
+typedef struct ngp_encoding* ngp_encoding_t;
+/* json: the "encoding" object of a network config (otype HashGrid, n_levels, n_features_per_level,
+ * log2_hashmap_size, base_resolution, per_level_scale) */
+int ngp_encoding_create(const char* json, uint32_t n_dims_to_encode, ngp_encoding_t* out);
+void ngp_encoding_destroy(ngp_encoding_t e);
+uint64_t ngp_encoding_n_params(ngp_encoding_t e);               /* Encoding::n_params() */
+uint32_t ngp_encoding_padded_output_width(ngp_encoding_t e);    /* Encoding::padded_output_width(), alignment 16 */
+/* level geometry: offsets[L+1] (entries), scales[L], resolutions[L]; any pointer may be NULL. returns n_levels */
+uint32_t ngp_encoding_level_table(ngp_encoding_t e, uint32_t* offsets, float* scales, uint32_t* resolutions);
+/* Encoding::initialize_params: U(-1e-4,1e-4), counter-based pcg32(seed) */
+int ngp_encoding_initialize_params(ngp_encoding_t e, void* stream, uint64_t seed, void* dev_params_fp32);
+/* Encoding::inference_mixed_precision / forward: x fp32 [n][x_stride], y fp16 [n][padded_width] in y_layout */
+int ngp_encoding_forward(ngp_encoding_t e, void* stream, const void* dev_params_fp16, const void* dev_x, uint32_t x_stride,
+                         uint32_t n, void* dev_y, int y_layout);
+/* Encoding::backward, param gradients: dev_grad_fp16 (table shaped) += scatter(w * dy)  (EGradientMode::Accumulate;
+ * zero it first for Overwrite) */
+int ngp_encoding_backward(ngp_encoding_t e, void* stream, const void* dev_x, uint32_t x_stride, uint32_t n, const void* dev_dy,
+                          int dy_layout, void* dev_grad_fp16);
+/* Encoding::backward, input gradients (testbed_nerf.cu:2615-2617,4071-4078): dx fp32 [n][n_dims] */
+int ngp_encoding_backward_input(ngp_encoding_t e, void* stream, const void* dev_params_fp16, const void* dev_x, uint32_t x_stride,
+                                uint32_t n, const void* dev_dy, int dy_layout, void* dev_dx);
+/* parity hook: level-local corner indices uint32 [n][2^D] and fp32 weights [n][2^D] of one level */
+int ngp_encoding_corners(ngp_encoding_t e, void* stream, const void* dev_x, uint32_t x_stride, uint32_t n, uint32_t level,
+                         void* dev_idx, void* dev_w);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * NerfNetwork  —  replaces ngp::NerfNetwork<T> (include/neural-graphics-primitives/nerf_network.h:76-578)
+ * json: full network config with "encoding", "network", "dir_encoding", "rgb_network" (configs/nerf/base.json)
+ * ------------------------------------------------------------------------------------------------------------ */
+typedef struct ngp_nerf_network* ngp_nerf_network_t;
+int ngp_nerf_network_create(const char* json, ngp_nerf_network_t* out);
+void ngp_nerf_network_destroy(ngp_nerf_network_t n);
+uint64_t ngp_nerf_network_n_params(ngp_nerf_network_t n);                   /* nerf_network.h:459-461 */
+/* flat layout (nerf_network.h:430-443): offsets of density MLP, rgb MLP, position encoding; n_matrix = MLP params */
+int ngp_nerf_network_layout(ngp_nerf_network_t n, uint64_t* off_density, uint64_t* off_rgb, uint64_t* off_encoding, uint64_t* n_matrix_params);
+int ngp_nerf_network_initialize_params(ngp_nerf_network_t n, void* stream, uint64_t seed, void* dev_params_fp32);  /* :445-457 */
+/* inference_mixed_precision_impl (:116-173): coords fp32 [n][7] = (pos3, dt, dir3); out fp16 [n][4] = (r,g,b,sigma) raw.
+ * n must be a multiple of 128 (callers round to NGP_BATCH_GRANULARITY like the reference). */
+int ngp_nerf_network_inference(ngp_nerf_network_t n, void* stream, const void* dev_params_fp16, const void* dev_coords, uint32_t count, void* dev_out);
+/* density() (:337-353): pos fp32 [n][pos_stride]; out fp16 [n] */
+int ngp_nerf_network_density(ngp_nerf_network_t n, void* stream, const void* dev_params_fp16, const void* dev_pos, uint32_t pos_stride, uint32_t count, void* dev_out);
+/* forward_impl + backward_impl with EGradientMode::Overwrite (:179-335): dL_dout fp16 [n][4]; grads fp16, param shaped */
+int ngp_nerf_network_forward_backward(ngp_nerf_network_t n, void* stream, const void* dev_params_fp16, const void* dev_coords, uint32_t count,
+                                      const void* dev_dL_dout, void* dev_grads_fp16);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * NetworkWithInputEncoding — replaces tcnn::NetworkWithInputEncoding<T> (src/testbed.cu:4101-4113; image/SDF modes)
+ * ------------------------------------------------------------------------------------------------------------ */
+typedef struct ngp_encoded_mlp* ngp_encoded_mlp_t;
+int ngp_encoded_mlp_create(const char* json, uint32_t n_input_dims, uint32_t n_output_dims, ngp_encoded_mlp_t* out);
+void ngp_encoded_mlp_destroy(ngp_encoded_mlp_t m);
+uint64_t ngp_encoded_mlp_n_params(ngp_encoded_mlp_t m);
+int ngp_encoded_mlp_layout(ngp_encoded_mlp_t m, uint64_t* off_mlp, uint64_t* off_encoding, uint64_t* n_matrix_params);
+int ngp_encoded_mlp_initialize_params(ngp_encoded_mlp_t m, void* stream, uint64_t seed, void* dev_params_fp32);
+/* x fp32 [n][x_stride]; out fp16 [n][16] (first n_output_dims meaningful) */
+int ngp_encoded_mlp_inference(ngp_encoded_mlp_t m, void* stream, const void* dev_params_fp16, const void* dev_x, uint32_t x_stride, uint32_t count, void* dev_out);
+int ngp_encoded_mlp_forward_backward(ngp_encoded_mlp_t m, void* stream, const void* dev_params_fp16, const void* dev_x, uint32_t x_stride, uint32_t count,
+                                     const void* dev_dL_dout /* fp16 [n][16] */, void* dev_grads_fp16);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Optimizer step — replaces tcnn::Trainer::optimizer_step -> Ema(ExponentialDecay(Adam)) (src/testbed_nerf.cu:3678,
+ * src/testbed_image.cu:283).  Stateless form: the caller owns all buffers.
+ * ------------------------------------------------------------------------------------------------------------ */
+typedef struct ngp_adam_hyper {
+    float learning_rate, beta1, beta2, epsilon, l2_reg, loss_scale;
+    uint64_t n_matrix_params;
+    int32_t optimize_matrix_params, optimize_non_matrix_params;
+    float ema_decay;      /* 0 = no EMA */
+    uint32_t ema_step;    /* 1-based */
+} ngp_adam_hyper;
+int ngp_adam_step(void* stream, const ngp_adam_hyper* h, uint64_t n, void* dev_master_fp32, void* dev_params_fp16, const void* dev_grads_fp16,
+                  void* dev_m_fp32, void* dev_v_fp32, void* dev_steps_u32, void* dev_ema_fp32 /* nullable */, void* dev_ema_fp16 /* nullable */);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NGP_B200_H */

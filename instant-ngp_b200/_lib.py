@@ -1,0 +1,82 @@
+"""ctypes loader for libngp_b200.so (the C ABI declared in include/ngp_b200.h).
+
+The product path has NO fallback: if the shared library is missing or a call fails, a RuntimeError is raised
+(the reference raises std::runtime_error through pybind11 -> RuntimeError, main.cu:195-209).
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libngp_b200.so")
+
+_lib = None
+
+
+class NgpError(RuntimeError):
+    pass
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise NgpError(f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                           "(there is no CPU fallback)")
+        _lib = C.CDLL(LIB_PATH)
+        _declare(_lib)
+    return _lib
+
+
+def check(status):
+    if status != 0:
+        raise NgpError(lib().ngp_last_error().decode())
+
+
+u32, u64, i32, f32, vp, cp = C.c_uint32, C.c_uint64, C.c_int, C.c_float, C.c_void_p, C.c_char_p
+
+
+class AdamHyper(C.Structure):
+    _fields_ = [("learning_rate", f32), ("beta1", f32), ("beta2", f32), ("epsilon", f32), ("l2_reg", f32), ("loss_scale", f32),
+                ("n_matrix_params", u64), ("optimize_matrix_params", C.c_int32), ("optimize_non_matrix_params", C.c_int32),
+                ("ema_decay", f32), ("ema_step", u32)]
+
+
+# name -> (restype, argtypes); every symbol include/ngp_b200.h declares
+SYMBOLS = {
+    "ngp_last_error": (cp, []),
+    "ngp_abi_version": (i32, []),
+    "ngp_kernel_launch_count": (u64, []),
+    "ngp_encoding_create": (i32, [cp, u32, C.POINTER(vp)]),
+    "ngp_encoding_destroy": (None, [vp]),
+    "ngp_encoding_n_params": (u64, [vp]),
+    "ngp_encoding_padded_output_width": (u32, [vp]),
+    "ngp_encoding_level_table": (u32, [vp, C.POINTER(u32), C.POINTER(f32), C.POINTER(u32)]),
+    "ngp_encoding_initialize_params": (i32, [vp, vp, u64, vp]),
+    "ngp_encoding_forward": (i32, [vp, vp, vp, vp, u32, u32, vp, i32]),
+    "ngp_encoding_backward": (i32, [vp, vp, vp, u32, u32, vp, i32, vp]),
+    "ngp_encoding_backward_input": (i32, [vp, vp, vp, vp, u32, u32, vp, i32, vp]),
+    "ngp_encoding_corners": (i32, [vp, vp, vp, u32, u32, u32, vp, vp]),
+    "ngp_nerf_network_create": (i32, [cp, C.POINTER(vp)]),
+    "ngp_nerf_network_destroy": (None, [vp]),
+    "ngp_nerf_network_n_params": (u64, [vp]),
+    "ngp_nerf_network_layout": (i32, [vp, C.POINTER(u64), C.POINTER(u64), C.POINTER(u64), C.POINTER(u64)]),
+    "ngp_nerf_network_initialize_params": (i32, [vp, vp, u64, vp]),
+    "ngp_nerf_network_inference": (i32, [vp, vp, vp, vp, u32, vp]),
+    "ngp_nerf_network_density": (i32, [vp, vp, vp, vp, u32, u32, vp]),
+    "ngp_nerf_network_forward_backward": (i32, [vp, vp, vp, vp, u32, vp, vp]),
+    "ngp_encoded_mlp_create": (i32, [cp, u32, u32, C.POINTER(vp)]),
+    "ngp_encoded_mlp_destroy": (None, [vp]),
+    "ngp_encoded_mlp_n_params": (u64, [vp]),
+    "ngp_encoded_mlp_layout": (i32, [vp, C.POINTER(u64), C.POINTER(u64), C.POINTER(u64)]),
+    "ngp_encoded_mlp_initialize_params": (i32, [vp, vp, u64, vp]),
+    "ngp_encoded_mlp_inference": (i32, [vp, vp, vp, vp, u32, u32, vp]),
+    "ngp_encoded_mlp_forward_backward": (i32, [vp, vp, vp, vp, u32, u32, vp, vp]),
+    "ngp_adam_step": (i32, [vp, C.POINTER(AdamHyper), u64, vp, vp, vp, vp, vp, vp, vp, vp]),
+}
+
+
+def _declare(l):
+    for name, (res, args) in SYMBOLS.items():
+        fn = getattr(l, name)   # AttributeError here == ABI drift: fail loudly
+        fn.restype = res
+        fn.argtypes = args

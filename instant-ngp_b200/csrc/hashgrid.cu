@@ -1,0 +1,304 @@
+// Multiresolution hash-grid encoding for sm_100a: forward gather + D-linear interpolation, backward scatter-add,
+// input gradients.  Replaces tcnn::GridEncoding<__half> behind the reference's NerfNetwork / NetworkWithInputEncoding
+// (nerf_network.h:93-95,143-148,324-333; testbed.cu:3961-4005,4101).
+//
+// Bottleneck: random 4..16-byte gathers (one 32 B L2 sector per corner), L2-latency/LTS-throughput bound when the
+// table fits B200's 126 MB L2 and HBM-sector bound otherwise.  Mapping: one thread per (point, 8-feature chunk) —
+// a chunk is 8/F consecutive levels — so every thread keeps (8/F)*2^D independent vector loads in flight and the
+// warp's result is written as full 16-byte chunks of the blk8 activation layout (ngp_common.cuh) that the tcgen05
+// MLP kernels pull in with one bulk-async copy per 128-sample tile.
+#include "ngp_internal.h"
+#include <cmath>
+#include <algorithm>
+
+namespace ngp {
+
+void grid_make_layout(GridLayout& g, uint32_t n_dims, uint32_t n_levels, uint32_t n_features, uint32_t log2T,
+                      uint32_t base_resolution, float per_level_scale) {
+    NGP_CHECK(n_dims == 2 || n_dims == 3, "HashGrid: n_pos_dims must be 2 or 3");
+    NGP_CHECK(n_levels >= 1 && n_levels <= GRID_MAX_LEVELS, "HashGrid: n_levels must be in [1,32]");
+    NGP_CHECK(n_features == 1 || n_features == 2 || n_features == 4 || n_features == 8, "HashGrid: n_features_per_level must be 1,2,4 or 8");
+    NGP_CHECK(log2T >= 4 && log2T <= 28, "HashGrid: log2_hashmap_size out of range");
+    g = GridLayout{};
+    g.n_dims = n_dims; g.n_levels = n_levels; g.n_features = n_features; g.log2_hashmap_size = log2T;
+    g.base_resolution = base_resolution; g.per_level_scale = per_level_scale;
+    g.padded_width = (uint32_t)next_multiple(n_levels * n_features, 16);
+    NGP_CHECK(g.padded_width <= 64, "HashGrid: n_levels*n_features_per_level must be <= 64");
+    // Level geometry is computed ONCE on the host so that device code and the CPU oracle see identical floats.
+    float log2b = std::log2(per_level_scale);
+    uint32_t offset = 0;
+    for (uint32_t l = 0; l < n_levels; ++l) {
+        float scale = exp2f((float)l * log2b) * (float)base_resolution - 1.0f;
+        uint32_t res = (uint32_t)ceilf(scale) + 1u;
+        uint32_t max_params = 0xFFFFFFFFu / 2;
+        double dense = std::pow((double)res, (double)n_dims);
+        uint32_t n = dense > (double)max_params ? max_params : (uint32_t)(dense + 0.5);
+        n = (n + GRID_PARAM_ALIGN - 1) / GRID_PARAM_ALIGN * GRID_PARAM_ALIGN;
+        n = std::min(n, 1u << log2T);
+        g.offsets[l] = offset; g.sizes[l] = n; g.resolutions[l] = res; g.scales[l] = scale;
+        // the (uint32-wrapping) stride walk of the index function does not depend on the cell: do it here
+        uint32_t stride = 1;
+        for (uint32_t d = 0; d < n_dims && stride <= n; ++d) { g.dense_stride[l][d] = stride; stride *= res; }
+        if (n < stride) g.hashed_mask |= 1u << l;
+        offset += n;
+    }
+    g.offsets[n_levels] = offset;
+    g.n_params = (uint64_t)offset * n_features;
+}
+
+// ------------------------------------------------------------------------------------------------
+template <uint32_t D>
+struct Cell { uint32_t c[D]; float f[D]; };
+
+template <uint32_t D>
+NGP_D Cell<D> locate(const float* __restrict__ x, float scale) {
+    Cell<D> r;
+#pragma unroll
+    for (uint32_t d = 0; d < D; ++d) {
+        float p = fmaf(scale, x[d], 0.5f);
+        float fl = floorf(p);
+        r.c[d] = (uint32_t)(int)fl;
+        r.f[d] = p - fl;
+    }
+    return r;
+}
+
+template <uint32_t D>
+NGP_D uint32_t corner_index(const GridLayout& g, uint32_t level, const Cell<D>& cell, uint32_t corner, float& w) {
+    uint32_t cl[D];
+    w = 1.0f;
+#pragma unroll
+    for (uint32_t d = 0; d < D; ++d) {
+        if ((corner & (1u << d)) == 0) { w *= 1.0f - cell.f[d]; cl[d] = cell.c[d]; }
+        else { w *= cell.f[d]; cl[d] = cell.c[d] + 1; }
+    }
+    const uint32_t size = g.sizes[level];
+    uint32_t index;
+    if (g.hashed_mask & (1u << level)) {
+        index = cl[0];
+        if (D > 1) index ^= cl[1] * GRID_PRIME_1;
+        if (D > 2) index ^= cl[2] * GRID_PRIME_2;
+        index &= size - 1;   // hashed levels always have size == 2^log2_hashmap_size
+    } else {
+        index = 0;
+#pragma unroll
+        for (uint32_t d = 0; d < D; ++d) index += cl[d] * g.dense_stride[level][d];
+        if (index >= size) index %= size;
+    }
+    return index;
+}
+
+template <uint32_t F> struct Feat;
+template <> struct Feat<1> { using T = unsigned short; };
+template <> struct Feat<2> { using T = uint32_t; };
+template <> struct Feat<4> { using T = uint2; };
+template <> struct Feat<8> { using T = uint4; };
+
+template <uint32_t F>
+NGP_D void accumulate(float* acc, float w, typename Feat<F>::T raw) {
+    const __half* h = reinterpret_cast<const __half*>(&raw);
+#pragma unroll
+    for (uint32_t f = 0; f < F; ++f) acc[f] = fmaf(w, __half2float(h[f]), acc[f]);
+}
+
+template <uint32_t D, uint32_t F>
+__global__ void __launch_bounds__(256) grid_forward_kernel(const GridLayout g, const __half* __restrict__ table, const float* __restrict__ x,
+                                                           uint32_t x_stride, uint32_t n, __half* __restrict__ y, int y_layout) {
+    constexpr uint32_t LPC = 8 / F;          // levels per 8-feature chunk
+    constexpr uint32_t NC = 1u << D;
+    const uint32_t chunks = g.padded_width / 8;
+    // consecutive threads: 8 rows x `chunks` chunks, rows fastest, so a warp's 16 B stores fill whole 128 B core matrices
+    const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t group = tid / (8 * chunks), in_group = tid % (8 * chunks);
+    const uint32_t row = group * 8 + (in_group & 7), chunk = in_group >> 3;
+    if (row >= n) return;
+    const float* xp = x + (size_t)row * x_stride;
+    float acc[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] = 0.0f;
+#pragma unroll
+    for (uint32_t li = 0; li < LPC; ++li) {
+        const uint32_t level = chunk * LPC + li;
+        if (level >= g.n_levels) break;
+        const Cell<D> cell = locate<D>(xp, g.scales[level]);
+        const typename Feat<F>::T* t = reinterpret_cast<const typename Feat<F>::T*>(table) + g.offsets[level];
+        typename Feat<F>::T raw[NC]; float w[NC];
+#pragma unroll
+        for (uint32_t k = 0; k < NC; ++k) raw[k] = __ldg(t + corner_index<D>(g, level, cell, k, w[k]));
+#pragma unroll
+        for (uint32_t k = 0; k < NC; ++k) accumulate<F>(acc + li * F, w[k], raw[k]);
+    }
+    __half2 o[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) o[i] = __floats2half2_rn(acc[2 * i], acc[2 * i + 1]);
+    size_t off = (y_layout == LAYOUT_BLK8) ? blk8_chunk_offset(row, chunk, g.padded_width) : (size_t)row * g.padded_width + chunk * 8;
+    *reinterpret_cast<uint4*>(y + off) = *reinterpret_cast<const uint4*>(o);
+}
+
+// vector reductions into the fp16 gradient table (RED.E.ADD.F16x2; one instruction per table entry)
+NGP_D void red_add_h2(__half* p, float a, float b) { atomicAdd(reinterpret_cast<__half2*>(p), __floats2half2_rn(a, b)); }
+NGP_D void red_add_h4(__half* p, float a, float b, float c, float d) {
+    __half2 lo = __floats2half2_rn(a, b), hi = __floats2half2_rn(c, d);
+    asm volatile("red.global.add.noftz.v2.f16x2 [%0], {%1, %2};" ::"l"(p), "r"(*reinterpret_cast<uint32_t*>(&lo)), "r"(*reinterpret_cast<uint32_t*>(&hi)) : "memory");
+}
+
+template <uint32_t D, uint32_t F>
+__global__ void __launch_bounds__(256) grid_backward_kernel(const GridLayout g, const float* __restrict__ x, uint32_t x_stride, uint32_t n,
+                                                            const __half* __restrict__ dy, int dy_layout, __half* __restrict__ grad) {
+    constexpr uint32_t LPC = 8 / F;
+    constexpr uint32_t NC = 1u << D;
+    const uint32_t chunks = g.padded_width / 8;
+    const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t group = tid / (8 * chunks), in_group = tid % (8 * chunks);
+    const uint32_t row = group * 8 + (in_group & 7), chunk = in_group >> 3;
+    if (row >= n) return;
+    size_t off = (dy_layout == LAYOUT_BLK8) ? blk8_chunk_offset(row, chunk, g.padded_width) : (size_t)row * g.padded_width + chunk * 8;
+    const uint4 raw = __ldg(reinterpret_cast<const uint4*>(dy + off));
+    if ((raw.x | raw.y | raw.z | raw.w) == 0u) return;   // padding rows / untouched levels contribute nothing
+    const __half* dh = reinterpret_cast<const __half*>(&raw);
+    const float* xp = x + (size_t)row * x_stride;
+#pragma unroll
+    for (uint32_t li = 0; li < LPC; ++li) {
+        const uint32_t level = chunk * LPC + li;
+        if (level >= g.n_levels) break;
+        float d[F]; bool any = false;
+#pragma unroll
+        for (uint32_t f = 0; f < F; ++f) { d[f] = __half2float(dh[li * F + f]); any |= d[f] != 0.0f; }
+        if (!any) continue;
+        const Cell<D> cell = locate<D>(xp, g.scales[level]);
+        __half* gl = grad + (size_t)g.offsets[level] * F;
+#pragma unroll
+        for (uint32_t k = 0; k < NC; ++k) {
+            float w; const uint32_t idx = corner_index<D>(g, level, cell, k, w);
+            __half* p = gl + (size_t)idx * F;
+            if (F == 1) atomicAdd(p, __float2half_rn(w * d[0]));
+            else if (F == 2) red_add_h2(p, w * d[0], w * d[1]);
+            else if (F == 4) red_add_h4(p, w * d[0], w * d[1], w * d[2], w * d[3]);
+            else { red_add_h4(p, w * d[0], w * d[1], w * d[2], w * d[3]); red_add_h4(p + 4, w * d[4 % F], w * d[5 % F], w * d[6 % F], w * d[7 % F]); }
+        }
+    }
+}
+
+// dL/dx_d = sum_levels scale_l * sum_{corner pairs along d} w_others * (v(c_d+1) - v(c_d)) . dy_l
+template <uint32_t D, uint32_t F>
+__global__ void __launch_bounds__(256) grid_backward_input_kernel(const GridLayout g, const __half* __restrict__ table, const float* __restrict__ x,
+                                                                  uint32_t x_stride, uint32_t n, const __half* __restrict__ dy, int dy_layout,
+                                                                  float* __restrict__ dx) {
+    constexpr uint32_t NC = 1u << D;
+    const uint32_t row = blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= n) return;
+    const float* xp = x + (size_t)row * x_stride;
+    float out[D];
+#pragma unroll
+    for (uint32_t d = 0; d < D; ++d) out[d] = 0.0f;
+    for (uint32_t level = 0; level < g.n_levels; ++level) {
+        const Cell<D> cell = locate<D>(xp, g.scales[level]);
+        const __half* t = table + (size_t)g.offsets[level] * F;
+        float v[NC][F];
+#pragma unroll
+        for (uint32_t k = 0; k < NC; ++k) {
+            float w; const uint32_t idx = corner_index<D>(g, level, cell, k, w);
+#pragma unroll
+            for (uint32_t f = 0; f < F; ++f) v[k][f] = __half2float(t[(size_t)idx * F + f]);
+        }
+        float dyl[F];
+#pragma unroll
+        for (uint32_t f = 0; f < F; ++f) {
+            const uint32_t c = level * F + f;
+            size_t off = (dy_layout == LAYOUT_BLK8) ? blk8_offset(row, c, g.padded_width) : (size_t)row * g.padded_width + c;
+            dyl[f] = __half2float(dy[off]);
+        }
+#pragma unroll
+        for (uint32_t gd = 0; gd < D; ++gd) {
+            float acc = 0.0f;
+#pragma unroll
+            for (uint32_t k = 0; k < NC; ++k) {
+                if (k & (1u << gd)) continue;
+                float wo = 1.0f;
+#pragma unroll
+                for (uint32_t d = 0; d < D; ++d) if (d != gd) wo *= (k & (1u << d)) ? cell.f[d] : 1.0f - cell.f[d];
+#pragma unroll
+                for (uint32_t f = 0; f < F; ++f) acc += wo * (v[k | (1u << gd)][f] - v[k][f]) * dyl[f];
+            }
+            out[gd] += acc * g.scales[level];
+        }
+    }
+#pragma unroll
+    for (uint32_t d = 0; d < D; ++d) dx[(size_t)row * D + d] = out[d];
+}
+
+template <uint32_t D>
+__global__ void grid_corners_kernel(const GridLayout g, const float* __restrict__ x, uint32_t x_stride, uint32_t n, uint32_t level,
+                                    uint32_t* __restrict__ idx, float* __restrict__ wout) {
+    const uint32_t row = blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= n) return;
+    const Cell<D> cell = locate<D>(x + (size_t)row * x_stride, g.scales[level]);
+    for (uint32_t k = 0; k < (1u << D); ++k) {
+        float w; idx[(size_t)row * (1u << D) + k] = corner_index<D>(g, level, cell, k, w);
+        wout[(size_t)row * (1u << D) + k] = w;
+    }
+}
+
+__global__ void grid_init_kernel(uint64_t n, Pcg32 rng, float* __restrict__ p) {
+    const uint64_t i0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (i0 >= n) return;
+    rng.advance((int64_t)i0);
+    for (uint64_t i = i0; i < i0 + 4 && i < n; ++i) p[i] = rng.next_float() * (2.0f * GRID_INIT_RANGE) - GRID_INIT_RANGE;
+}
+
+#define GRID_DISPATCH(KERNEL, ...)                                                                      \
+    do {                                                                                                 \
+        const uint32_t key = g.n_dims * 16 + g.n_features;                                               \
+        switch (key) {                                                                                   \
+            case 2 * 16 + 1: KERNEL<2, 1><<<blocks, 256, 0, s>>>(__VA_ARGS__); break;                   \
+            case 2 * 16 + 2: KERNEL<2, 2><<<blocks, 256, 0, s>>>(__VA_ARGS__); break;                   \
+            case 2 * 16 + 4: KERNEL<2, 4><<<blocks, 256, 0, s>>>(__VA_ARGS__); break;                   \
+            case 2 * 16 + 8: KERNEL<2, 8><<<blocks, 256, 0, s>>>(__VA_ARGS__); break;                   \
+            case 3 * 16 + 1: KERNEL<3, 1><<<blocks, 256, 0, s>>>(__VA_ARGS__); break;                   \
+            case 3 * 16 + 2: KERNEL<3, 2><<<blocks, 256, 0, s>>>(__VA_ARGS__); break;                   \
+            case 3 * 16 + 4: KERNEL<3, 4><<<blocks, 256, 0, s>>>(__VA_ARGS__); break;                   \
+            case 3 * 16 + 8: KERNEL<3, 8><<<blocks, 256, 0, s>>>(__VA_ARGS__); break;                   \
+            default: throw Error("HashGrid: unsupported (n_dims, n_features_per_level)");               \
+        }                                                                                                \
+        NGP_POST_LAUNCH();                                                              \
+    } while (0)
+
+void grid_forward(cudaStream_t s, const GridLayout& g, const __half* table, const float* x, uint32_t x_stride, uint32_t n,
+                  __half* y, int y_layout) {
+    if (n == 0) return;
+    const uint32_t threads = (uint32_t)next_multiple(n, 8) * (g.padded_width / 8);
+    const uint32_t blocks = div_round_up(threads, 256);
+    GRID_DISPATCH(grid_forward_kernel, g, table, x, x_stride, n, y, y_layout);
+}
+
+void grid_backward(cudaStream_t s, const GridLayout& g, const float* x, uint32_t x_stride, uint32_t n, const __half* dy,
+                   int dy_layout, __half* grad) {
+    if (n == 0) return;
+    const uint32_t threads = (uint32_t)next_multiple(n, 8) * (g.padded_width / 8);
+    const uint32_t blocks = div_round_up(threads, 256);
+    GRID_DISPATCH(grid_backward_kernel, g, x, x_stride, n, dy, dy_layout, grad);
+}
+
+void grid_backward_input(cudaStream_t s, const GridLayout& g, const __half* table, const float* x, uint32_t x_stride,
+                         uint32_t n, const __half* dy, int dy_layout, float* dx) {
+    if (n == 0) return;
+    const uint32_t blocks = div_round_up(n, 256);
+    GRID_DISPATCH(grid_backward_input_kernel, g, table, x, x_stride, n, dy, dy_layout, dx);
+}
+
+void grid_corners(cudaStream_t s, const GridLayout& g, const float* x, uint32_t x_stride, uint32_t n, uint32_t level,
+                  uint32_t* idx, float* w) {
+    NGP_CHECK(level < g.n_levels, "grid_corners: level out of range");
+    if (n == 0) return;
+    if (g.n_dims == 2) grid_corners_kernel<2><<<div_round_up(n, 256), 256, 0, s>>>(g, x, x_stride, n, level, idx, w);
+    else grid_corners_kernel<3><<<div_round_up(n, 256), 256, 0, s>>>(g, x, x_stride, n, level, idx, w);
+    NGP_POST_LAUNCH();
+}
+
+void grid_init(cudaStream_t s, const GridLayout& g, Pcg32 rng, float* params) {
+    const uint64_t n = g.n_params;
+    grid_init_kernel<<<(uint32_t)((n / 4 + 255) / 256 + 1), 256, 0, s>>>(n, rng, params);
+    NGP_POST_LAUNCH();
+}
+
+}  // namespace ngp

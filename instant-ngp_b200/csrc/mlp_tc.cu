@@ -1,0 +1,597 @@
+// Fully fused 64-neuron MLPs on the 5th-generation tensor cores (tcgen05.mma, accumulators in TMEM).
+// Replaces tcnn::FullyFusedMLP<__half,64> and the NerfNetwork glue kernels extract_density / extract_rgb /
+// add_density_gradient (nerf_network.h:31-74) — the whole density-MLP -> [density16 | SH16] -> rgb-MLP chain runs
+// per 128-sample tile with every activation resident in shared memory, input tiles fed by bulk-async (TMA) copies.
+//
+// Structure (one warpgroup = 128 threads per CTA, several CTAs per SM, persistent over tiles):
+//   thread 0 issues tcgen05.mma for a layer and commits to an mbarrier; all 128 threads wait, then thread t reads
+//   TMEM lane t (= sample row t of the tile) with tcgen05.ld, applies ReLU, rounds to fp16 (the same storage points
+//   as the reference's fp16 activations) and writes its row as 16-byte chunks into the next layer's operand tile.
+#include "ngp_internal.h"
+#include "tc05.cuh"
+
+namespace ngp {
+using namespace tc;
+
+// ---- shared-memory carve-up helpers ---------------------------------------------------------------------------
+struct SmemCursor {
+    uint32_t off = 0;
+    __host__ __device__ uint32_t take(uint32_t bytes) { uint32_t o = off; off += (bytes + 127u) & ~127u; return o; }
+};
+
+// copy a row-major fp16 weight matrix [rows x cols] from global into a blk8 tile in shared memory
+NGP_D void load_weights_blk8(__half* dst, const __half* __restrict__ src, uint32_t rows, uint32_t cols, uint32_t tid, uint32_t nthreads) {
+    const uint32_t cpr = cols >> 3;
+    for (uint32_t i = tid; i < rows * cpr; i += nthreads) {
+        const uint32_t r = i / cpr, c = i % cpr;
+        *reinterpret_cast<uint4*>(dst + blk8_chunk_offset(r, c, cols)) = __ldg(reinterpret_cast<const uint4*>(src + (size_t)r * cols + c * 8));
+    }
+}
+
+NGP_D uint4 pack8(const float* v, bool relu) {
+    __half2 h[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        float a = v[2 * i], b = v[2 * i + 1];
+        if (relu) { a = fmaxf(a, 0.0f); b = fmaxf(b, 0.0f); }
+        h[i] = __floats2half2_rn(a, b);
+    }
+    return *reinterpret_cast<uint4*>(h);
+}
+
+// TMEM accumulator [128 x N] (row = this thread) -> fp16 blk8 tile `dst` (C_dst columns) at column c0
+template <uint32_t N, bool RELU>
+NGP_D void epilogue_to_smem(uint32_t tmem_row_addr, __half* dst, uint32_t C_dst, uint32_t c0, uint32_t row) {
+#pragma unroll
+    for (uint32_t j = 0; j < N; j += 16) {
+        float v[16];
+        tmem_ld16(tmem_row_addr + j, v);
+        tmem_wait_ld();
+        *reinterpret_cast<uint4*>(dst + blk8_chunk_offset(row, (c0 + j) >> 3, C_dst)) = pack8(v, RELU);
+        *reinterpret_cast<uint4*>(dst + blk8_chunk_offset(row, ((c0 + j) >> 3) + 1, C_dst)) = pack8(v + 8, RELU);
+    }
+}
+
+// SH degree 4 of 2*d-1 (replaces tcnn SphericalHarmonicsEncoding under Composite; configs/nerf/base.json:37-49)
+NGP_D void sh4(float dx, float dy, float dz, float* o) {
+    const float x = dx * 2.f - 1.f, y = dy * 2.f - 1.f, z = dz * 2.f - 1.f;
+    const float xy = x * y, xz = x * z, yz = y * z, x2 = x * x, y2 = y * y, z2 = z * z;
+    o[0] = 0.28209479177387814f;
+    o[1] = -0.48860251190291987f * y;
+    o[2] = 0.48860251190291987f * z;
+    o[3] = -0.48860251190291987f * x;
+    o[4] = 1.0925484305920792f * xy;
+    o[5] = -1.0925484305920792f * yz;
+    o[6] = 0.94617469575755997f * z2 - 0.31539156525251999f;
+    o[7] = -1.0925484305920792f * xz;
+    o[8] = 0.54627421529603959f * x2 - 0.54627421529603959f * y2;
+    o[9] = 0.59004358992664352f * y * (-3.0f * x2 + y2);
+    o[10] = 2.8906114426405538f * xy * z;
+    o[11] = 0.45704579946446572f * y * (1.0f - 5.0f * z2);
+    o[12] = 0.3731763325901154f * z * (5.0f * z2 - 3.0f);
+    o[13] = 0.45704579946446572f * x * (1.0f - 5.0f * z2);
+    o[14] = 1.4453057213202769f * z * (x2 - y2);
+    o[15] = 0.59004358992664352f * x * (-x2 + 3.0f * y2);
+}
+
+// One MMA stage: make this thread's smem writes visible to the async proxy, sync the CTA, let thread 0 issue.
+// `issue` is a lambda run by thread 0 only.  All threads return once the MMAs have completed.
+struct StageSync {
+    uint64_t* bar; uint32_t parity;
+    template <class F>
+    NGP_D void run(F&& issue) {
+        fence_proxy_async();
+        fence_before_sync();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            fence_after_sync();
+            issue();
+            umma_commit(bar);
+        }
+        mbar_wait(bar, parity);
+        parity ^= 1u;
+        fence_after_sync();
+    }
+};
+
+enum MlpMode : int { MODE_NERF = 0, MODE_DENSITY = 1, MODE_PLAIN = 2 };
+
+struct FwdParams {
+    const __half* w_density; const __half* w_rgb;
+    const __half* enc;        // [n x PW] blk8
+    const float* coords;      // [n][7] (MODE_NERF)
+    __half* out; uint32_t out_stride;
+    uint32_t n_tiles;
+};
+
+template <uint32_t PW, uint32_t DH, uint32_t RH, int MODE>
+struct FwdSmem {
+    // byte offsets from the 128 B aligned dynamic smem base
+    uint32_t wd[DH + 1], wr[RH + 1], x0[2], ha, hb, r0, bars, total;
+    __host__ __device__ FwdSmem() {
+        SmemCursor c;
+        wd[0] = c.take(MLP_WIDTH * PW * 2);
+        for (uint32_t l = 1; l < DH; ++l) wd[l] = c.take(MLP_WIDTH * MLP_WIDTH * 2);
+        wd[DH] = c.take(MLP_OUT_PAD * MLP_WIDTH * 2);
+        if (MODE == MODE_NERF) {
+            wr[0] = c.take(MLP_WIDTH * 32 * 2);
+            for (uint32_t l = 1; l < RH; ++l) wr[l] = c.take(MLP_WIDTH * MLP_WIDTH * 2);
+            wr[RH] = c.take(MLP_OUT_PAD * MLP_WIDTH * 2);
+            r0 = c.take(TILE_ROWS * 32 * 2);
+        } else { for (uint32_t l = 0; l <= RH; ++l) wr[l] = 0; r0 = 0; }
+        x0[0] = c.take(TILE_ROWS * PW * 2); x0[1] = c.take(TILE_ROWS * PW * 2);
+        ha = c.take(TILE_ROWS * MLP_WIDTH * 2); hb = c.take(TILE_ROWS * MLP_WIDTH * 2);
+        bars = c.take(64);
+        total = c.off + 128;
+    }
+};
+
+template <uint32_t PW, uint32_t DH, uint32_t RH, int MODE>
+__global__ void __launch_bounds__(128) mlp_forward_kernel(const FwdParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);
+    const FwdSmem<PW, DH, RH, MODE> L;
+    const uint32_t tid = threadIdx.x, warp = tid >> 5;
+    uint64_t* bar_full = reinterpret_cast<uint64_t*>(smem + L.bars);       // [2]
+    uint64_t* bar_mma = bar_full + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_full + 3);
+
+    // ---- one-time setup: barriers, TMEM, weights ----
+    if (tid == 0) { mbar_init(&bar_full[0], 1); mbar_init(&bar_full[1], 1); mbar_init(bar_mma, 1); mbar_fence_init(); }
+    if (warp == 0) tmem_alloc<64>(tmem_slot);
+    {
+        uint32_t in_w = PW; const __half* w = p.w_density;
+        for (uint32_t l = 0; l <= DH; ++l) {
+            const uint32_t rows = (l == DH) ? MLP_OUT_PAD : MLP_WIDTH;
+            load_weights_blk8(reinterpret_cast<__half*>(smem + L.wd[l]), w, rows, in_w, tid, 128);
+            w += rows * in_w; in_w = MLP_WIDTH;
+        }
+        if (MODE == MODE_NERF) {
+            in_w = 32; w = p.w_rgb;
+            for (uint32_t l = 0; l <= RH; ++l) {
+                const uint32_t rows = (l == RH) ? MLP_OUT_PAD : MLP_WIDTH;
+                load_weights_blk8(reinterpret_cast<__half*>(smem + L.wr[l]), w, rows, in_w, tid, 128);
+                w += rows * in_w; in_w = MLP_WIDTH;
+            }
+        }
+    }
+    fence_proxy_async();
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t tmem_row = tmem_base + ((warp * 32u) << 16);   // this warp's lane quadrant, column 0
+
+    const uint32_t sbase = smem_u32(smem);
+    const Operand X0[2] = {{sbase + L.x0[0], PW}, {sbase + L.x0[1], PW}};
+    const Operand HA = {sbase + L.ha, MLP_WIDTH}, HB = {sbase + L.hb, MLP_WIDTH}, R0 = {sbase + L.r0, 32};
+    __half* ha = reinterpret_cast<__half*>(smem + L.ha);
+    __half* hb = reinterpret_cast<__half*>(smem + L.hb);
+    __half* r0 = reinterpret_cast<__half*>(smem + L.r0);
+    constexpr uint32_t X_BYTES = TILE_ROWS * PW * 2;
+
+    StageSync stage{bar_mma, 0};
+    uint32_t full_parity[2] = {0, 0};
+    uint32_t it = 0;
+    if (tid == 0 && blockIdx.x < p.n_tiles) {
+        mbar_expect_tx(&bar_full[0], X_BYTES);
+        bulk_g2s(smem + L.x0[0], p.enc + (size_t)blockIdx.x * TILE_ROWS * PW, X_BYTES, &bar_full[0]);
+    }
+    for (uint32_t tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++it) {
+        const uint32_t buf = it & 1;
+        const uint32_t next = tile + gridDim.x;
+        if (tid == 0 && next < p.n_tiles) {   // prefetch the next input tile (its buffer was released one iteration ago)
+            mbar_expect_tx(&bar_full[buf ^ 1], X_BYTES);
+            bulk_g2s(smem + L.x0[buf ^ 1], p.enc + (size_t)next * TILE_ROWS * PW, X_BYTES, &bar_full[buf ^ 1]);
+        }
+        const uint32_t row_g = tile * TILE_ROWS + tid;
+        float dir[3] = {0.f, 0.f, 0.f};
+        if (MODE == MODE_NERF) { const float* c = p.coords + (size_t)row_g * 7 + 4; dir[0] = __ldg(c); dir[1] = __ldg(c + 1); dir[2] = __ldg(c + 2); }
+        mbar_wait(&bar_full[buf], full_parity[buf]); full_parity[buf] ^= 1u;
+
+        // ---- density / plain network ----
+        stage.run([&] { gemm_act_wT<64>(tmem_base, X0[buf], 0, Operand{sbase + L.wd[0], PW}, PW); });
+        epilogue_to_smem<64, true>(tmem_row, ha, MLP_WIDTH, 0, tid);
+        bool in_a = true;
+        for (uint32_t l = 1; l < DH; ++l) {
+            stage.run([&] { gemm_act_wT<64>(tmem_base, in_a ? HA : HB, 0, Operand{sbase + L.wd[l], MLP_WIDTH}, MLP_WIDTH); });
+            epilogue_to_smem<64, true>(tmem_row, in_a ? hb : ha, MLP_WIDTH, 0, tid);
+            in_a = !in_a;
+        }
+        stage.run([&] { gemm_act_wT<16>(tmem_base, in_a ? HA : HB, 0, Operand{sbase + L.wd[DH], MLP_WIDTH}, MLP_WIDTH); });
+        float dout[16];
+        tmem_ld16(tmem_row, dout); tmem_wait_ld();
+        if (MODE == MODE_DENSITY) { p.out[row_g] = __float2half_rn(dout[0]); continue; }
+        if (MODE == MODE_PLAIN) {
+            uint4* o = reinterpret_cast<uint4*>(p.out + (size_t)row_g * p.out_stride);
+            o[0] = pack8(dout, false); o[1] = pack8(dout + 8, false);
+            continue;
+        }
+        // ---- rgb network: input = [density out (16) | SH4(dir) (16)] ----
+        const __half sigma = __float2half_rn(dout[0]);
+        *reinterpret_cast<uint4*>(r0 + blk8_chunk_offset(tid, 0, 32)) = pack8(dout, false);
+        *reinterpret_cast<uint4*>(r0 + blk8_chunk_offset(tid, 1, 32)) = pack8(dout + 8, false);
+        float sh[16]; sh4(dir[0], dir[1], dir[2], sh);
+        *reinterpret_cast<uint4*>(r0 + blk8_chunk_offset(tid, 2, 32)) = pack8(sh, false);
+        *reinterpret_cast<uint4*>(r0 + blk8_chunk_offset(tid, 3, 32)) = pack8(sh + 8, false);
+        stage.run([&] { gemm_act_wT<64>(tmem_base, R0, 0, Operand{sbase + L.wr[0], 32}, 32); });
+        epilogue_to_smem<64, true>(tmem_row, ha, MLP_WIDTH, 0, tid);
+        in_a = true;
+        for (uint32_t l = 1; l < RH; ++l) {
+            stage.run([&] { gemm_act_wT<64>(tmem_base, in_a ? HA : HB, 0, Operand{sbase + L.wr[l], MLP_WIDTH}, MLP_WIDTH); });
+            epilogue_to_smem<64, true>(tmem_row, in_a ? hb : ha, MLP_WIDTH, 0, tid);
+            in_a = !in_a;
+        }
+        stage.run([&] { gemm_act_wT<16>(tmem_base, in_a ? HA : HB, 0, Operand{sbase + L.wr[RH], MLP_WIDTH}, MLP_WIDTH); });
+        float rgb[16];
+        tmem_ld16(tmem_row, rgb); tmem_wait_ld();
+        __half2 o2[2] = {__floats2half2_rn(rgb[0], rgb[1]), __halves2half2(__float2half_rn(rgb[2]), sigma)};
+        *reinterpret_cast<uint2*>(p.out + (size_t)row_g * 4) = *reinterpret_cast<uint2*>(o2);
+    }
+    // ---- teardown ----
+    fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc<64>(tmem_base);
+}
+
+
+// =================================================================================================================
+// Backward: forward recompute (activations stay in shared memory) + dgrad chain + wgrad, all on tcgen05.
+//   dgrad  D[128 x in]  = G[128 x out] * W[out x in]      (A = G K-major, B = W MN-major)
+//   wgrad  dW[out x in] += G^T[out x 128] * In[128 x in]  (A = G MN-major, M = 64; B = In MN-major); output layers are
+//          accumulated transposed (dW^T[64 x 16] = In^T * G) because M = 16 is not a legal UMMA shape.
+// wgrad accumulators stay in TMEM for the CTA's lifetime and are flushed once with fp32 atomics.
+// =================================================================================================================
+struct BwdParams {
+    const __half* w_density; const __half* w_rgb;
+    const __half* enc; const float* coords;
+    const __half* dL_dout; uint32_t dout_stride;
+    __half* dL_denc;      // nullable
+    float* wgrad;         // [n_density_params + n_rgb_params] fp32, atomically accumulated
+    uint32_t n_tiles;
+};
+
+template <uint32_t PW, uint32_t DH, uint32_t RH, int MODE>
+struct BwdCfg {
+    static constexpr uint32_t ACC_D0 = 64;                                  // density layer-0 wgrad [64 x PW]
+    static constexpr uint32_t ACC_DH = ACC_D0 + PW;                         // density hidden wgrads, 64 cols each
+    static constexpr uint32_t ACC_DO = ACC_DH + 64 * (DH - 1);              // density output wgrad^T [64 x 16]
+    static constexpr uint32_t ACC_R0 = ACC_DO + 16;                         // rgb layer-0 wgrad [64 x 32]
+    static constexpr uint32_t ACC_RH = ACC_R0 + (MODE == MODE_NERF ? 32 : 0);
+    static constexpr uint32_t ACC_RO = ACC_RH + (MODE == MODE_NERF ? 64 * (RH - 1) : 0);
+    static constexpr uint32_t ACC_END = ACC_RO + (MODE == MODE_NERF ? 16 : 0);
+    static constexpr uint32_t TMEM_COLS = ACC_END <= 128 ? 128 : (ACC_END <= 256 ? 256 : 512);
+    static_assert(ACC_END <= 512, "network too large for the TMEM-resident wgrad accumulators");
+    uint32_t wd[DH + 1], wr[RH + 1], x0, hd[DH], hr[RH], r0, g, go, bars, total;
+    __host__ __device__ BwdCfg() {
+        SmemCursor c;
+        wd[0] = c.take(MLP_WIDTH * PW * 2);
+        for (uint32_t l = 1; l < DH; ++l) wd[l] = c.take(MLP_WIDTH * MLP_WIDTH * 2);
+        wd[DH] = c.take(MLP_OUT_PAD * MLP_WIDTH * 2);
+        for (uint32_t l = 0; l <= RH; ++l) wr[l] = 0;
+        for (uint32_t l = 0; l < RH; ++l) hr[l] = 0;
+        r0 = 0;
+        if (MODE == MODE_NERF) {
+            wr[0] = c.take(MLP_WIDTH * 32 * 2);
+            for (uint32_t l = 1; l < RH; ++l) wr[l] = c.take(MLP_WIDTH * MLP_WIDTH * 2);
+            wr[RH] = c.take(MLP_OUT_PAD * MLP_WIDTH * 2);
+            r0 = c.take(TILE_ROWS * 32 * 2);
+            for (uint32_t l = 0; l < RH; ++l) hr[l] = c.take(TILE_ROWS * MLP_WIDTH * 2);
+        }
+        x0 = c.take(TILE_ROWS * PW * 2);
+        for (uint32_t l = 0; l < DH; ++l) hd[l] = c.take(TILE_ROWS * MLP_WIDTH * 2);
+        g = c.take(TILE_ROWS * MLP_WIDTH * 2);
+        go = c.take(TILE_ROWS * 16 * 2);
+        bars = c.take(64);
+        total = c.off + 128;
+    }
+};
+
+// TMEM [128 x 64] dgrad result -> ReLU-masked by the saved activation tile -> fp16 G tile (in place over the old G)
+NGP_D void epilogue_masked(uint32_t tmem_row_addr, __half* g, const __half* act, uint32_t row) {
+#pragma unroll
+    for (uint32_t j = 0; j < 64; j += 16) {
+        float v[16];
+        tmem_ld16(tmem_row_addr + j, v);
+        tmem_wait_ld();
+#pragma unroll
+        for (uint32_t c = 0; c < 2; ++c) {
+            const size_t off = blk8_chunk_offset(row, (j >> 3) + c, MLP_WIDTH);
+            const uint4 a = *reinterpret_cast<const uint4*>(act + off);
+            const __half* ah = reinterpret_cast<const __half*>(&a);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) if (!(__half2float(ah[i]) > 0.0f)) v[c * 8 + i] = 0.0f;
+            *reinterpret_cast<uint4*>(g + off) = pack8(v + c * 8, false);
+        }
+    }
+}
+
+// Backward through one chain (H hidden layers, input tile IN of CIN columns).  On return, if NEED_DIN, the TMEM work
+// accumulator (cols [0, CIN)) holds dL/dIN for this tile.
+template <uint32_t H, uint32_t CIN, bool NEED_DIN>
+NGP_D void bwd_chain(StageSync& stage, uint32_t tmem_base, uint32_t tmem_row, uint32_t sbase, uint8_t* smem, uint32_t acc0, uint32_t acch,
+                     uint32_t acco, uint32_t in_off, const uint32_t* act_off, uint32_t g_off, uint32_t go_off, const uint32_t* w_off,
+                     uint32_t accumulate, uint32_t tid) {
+    const Operand G = {sbase + g_off, MLP_WIDTH}, GO = {sbase + go_off, 16}, IN = {sbase + in_off, CIN};
+    __half* g = reinterpret_cast<__half*>(smem + g_off);
+    {   // output layer: wgrad^T [64 x 16] += act[H-1]^T * GO ; dgrad [128 x 64] = GO * W_out
+        const Operand A = {sbase + act_off[H - 1], MLP_WIDTH}, W = {sbase + w_off[H], MLP_WIDTH};
+        stage.run([&] { gemm_pT_q<16>(tmem_base + acco, A, 0, GO, 0, accumulate); gemm_act_w<64>(tmem_base, GO, W, 16); });
+        epilogue_masked(tmem_row, g, reinterpret_cast<const __half*>(smem + act_off[H - 1]), tid);
+    }
+    for (uint32_t l = H - 1; l >= 1; --l) {   // hidden layer l: wgrad [64 x 64] += G^T * act[l-1] ; dgrad = G * W_l
+        const Operand A = {sbase + act_off[l - 1], MLP_WIDTH}, W = {sbase + w_off[l], MLP_WIDTH};
+        stage.run([&] { gemm_pT_q<64>(tmem_base + acch + 64 * (l - 1), G, 0, A, 0, accumulate); gemm_act_w<64>(tmem_base, G, W, 64); });
+        epilogue_masked(tmem_row, g, reinterpret_cast<const __half*>(smem + act_off[l - 1]), tid);
+    }
+    {   // first layer: wgrad [64 x CIN] += G^T * IN ; dgrad [128 x CIN] = G * W_0
+        const Operand W = {sbase + w_off[0], CIN};
+        stage.run([&] { gemm_pT_q<CIN>(tmem_base + acc0, G, 0, IN, 0, accumulate); if (NEED_DIN) gemm_act_w<CIN>(tmem_base, G, W, 64); });
+    }
+}
+
+// flush one TMEM wgrad accumulator (M = 64 layout: row m lives in lane 32*(m/16) + m%16) to global with fp32 atomics
+template <uint32_t N, bool TRANSPOSED>
+NGP_D void flush_wgrad(uint32_t tmem_row, uint32_t col, float* dst, uint32_t ld, uint32_t tid) {
+    const uint32_t lane = tid & 31, m = (tid >> 5) * 16 + lane;
+#pragma unroll
+    for (uint32_t j = 0; j < N; j += 16) {
+        float v[16];
+        tmem_ld16(tmem_row + col + j, v);
+        tmem_wait_ld();
+        if (lane < 16) {
+#pragma unroll
+            for (uint32_t i = 0; i < 16; ++i) {
+                float* p = TRANSPOSED ? dst + (size_t)(j + i) * ld + m : dst + (size_t)m * ld + (j + i);
+                atomicAdd(p, v[i]);
+            }
+        }
+    }
+}
+
+template <uint32_t PW, uint32_t DH, uint32_t RH, int MODE, bool NEED_DENC>
+__global__ void __launch_bounds__(128) mlp_backward_kernel(const BwdParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);
+    using Cfg = BwdCfg<PW, DH, RH, MODE>;
+    const Cfg L;
+    const uint32_t tid = threadIdx.x, warp = tid >> 5;
+    uint64_t* bar_full = reinterpret_cast<uint64_t*>(smem + L.bars);
+    uint64_t* bar_mma = bar_full + 1;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_full + 2);
+
+    if (tid == 0) { mbar_init(bar_full, 1); mbar_init(bar_mma, 1); mbar_fence_init(); }
+    if (warp == 0) tmem_alloc<Cfg::TMEM_COLS>(tmem_slot);
+    {
+        uint32_t in_w = PW; const __half* w = p.w_density;
+        for (uint32_t l = 0; l <= DH; ++l) {
+            const uint32_t rows = (l == DH) ? MLP_OUT_PAD : MLP_WIDTH;
+            load_weights_blk8(reinterpret_cast<__half*>(smem + L.wd[l]), w, rows, in_w, tid, 128);
+            w += rows * in_w; in_w = MLP_WIDTH;
+        }
+        if (MODE == MODE_NERF) {
+            in_w = 32; w = p.w_rgb;
+            for (uint32_t l = 0; l <= RH; ++l) {
+                const uint32_t rows = (l == RH) ? MLP_OUT_PAD : MLP_WIDTH;
+                load_weights_blk8(reinterpret_cast<__half*>(smem + L.wr[l]), w, rows, in_w, tid, 128);
+                w += rows * in_w; in_w = MLP_WIDTH;
+            }
+        }
+    }
+    fence_proxy_async();
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t tmem_row = tmem_base + ((warp * 32u) << 16);
+    const uint32_t sbase = smem_u32(smem);
+    constexpr uint32_t X_BYTES = TILE_ROWS * PW * 2;
+    __half* r0 = reinterpret_cast<__half*>(smem + L.r0);
+    __half* go = reinterpret_cast<__half*>(smem + L.go);
+
+    StageSync stage{bar_mma, 0};
+    uint32_t full_parity = 0, it = 0;
+    if (tid == 0 && blockIdx.x < p.n_tiles) {
+        mbar_expect_tx(bar_full, X_BYTES);
+        bulk_g2s(smem + L.x0, p.enc + (size_t)blockIdx.x * TILE_ROWS * PW, X_BYTES, bar_full);
+    }
+    for (uint32_t tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++it) {
+        const uint32_t row_g = tile * TILE_ROWS + tid;
+        const uint32_t accumulate = it > 0;
+        float dir[3] = {0.f, 0.f, 0.f};
+        if (MODE == MODE_NERF) { const float* c = p.coords + (size_t)row_g * 7 + 4; dir[0] = __ldg(c); dir[1] = __ldg(c + 1); dir[2] = __ldg(c + 2); }
+        mbar_wait(bar_full, full_parity); full_parity ^= 1u;
+
+        // ---- forward recompute: density / plain chain ----
+        stage.run([&] { gemm_act_wT<64>(tmem_base, Operand{sbase + L.x0, PW}, 0, Operand{sbase + L.wd[0], PW}, PW); });
+        epilogue_to_smem<64, true>(tmem_row, reinterpret_cast<__half*>(smem + L.hd[0]), MLP_WIDTH, 0, tid);
+        for (uint32_t l = 1; l < DH; ++l) {
+            stage.run([&] { gemm_act_wT<64>(tmem_base, Operand{sbase + L.hd[l - 1], MLP_WIDTH}, 0, Operand{sbase + L.wd[l], MLP_WIDTH}, MLP_WIDTH); });
+            epilogue_to_smem<64, true>(tmem_row, reinterpret_cast<__half*>(smem + L.hd[l]), MLP_WIDTH, 0, tid);
+        }
+        if (MODE == MODE_NERF) {
+            stage.run([&] { gemm_act_wT<16>(tmem_base, Operand{sbase + L.hd[DH - 1], MLP_WIDTH}, 0, Operand{sbase + L.wd[DH], MLP_WIDTH}, MLP_WIDTH); });
+            float dout[16];
+            tmem_ld16(tmem_row, dout); tmem_wait_ld();
+            *reinterpret_cast<uint4*>(r0 + blk8_chunk_offset(tid, 0, 32)) = pack8(dout, false);
+            *reinterpret_cast<uint4*>(r0 + blk8_chunk_offset(tid, 1, 32)) = pack8(dout + 8, false);
+            float sh[16]; sh4(dir[0], dir[1], dir[2], sh);
+            *reinterpret_cast<uint4*>(r0 + blk8_chunk_offset(tid, 2, 32)) = pack8(sh, false);
+            *reinterpret_cast<uint4*>(r0 + blk8_chunk_offset(tid, 3, 32)) = pack8(sh + 8, false);
+            // ---- forward recompute: rgb hidden layers (the rgb output itself is not needed) ----
+            stage.run([&] { gemm_act_wT<64>(tmem_base, Operand{sbase + L.r0, 32}, 0, Operand{sbase + L.wr[0], 32}, 32); });
+            epilogue_to_smem<64, true>(tmem_row, reinterpret_cast<__half*>(smem + L.hr[0]), MLP_WIDTH, 0, tid);
+            for (uint32_t l = 1; l < RH; ++l) {
+                stage.run([&] { gemm_act_wT<64>(tmem_base, Operand{sbase + L.hr[l - 1], MLP_WIDTH}, 0, Operand{sbase + L.wr[l], MLP_WIDTH}, MLP_WIDTH); });
+                epilogue_to_smem<64, true>(tmem_row, reinterpret_cast<__half*>(smem + L.hr[l]), MLP_WIDTH, 0, tid);
+            }
+            // ---- dL/d(rgb out): extract_rgb (nerf_network.h:45-60) — only channels 0..2 feed the rgb net ----
+            const uint2 graw = __ldg(reinterpret_cast<const uint2*>(p.dL_dout + (size_t)row_g * 4));
+            const __half* gh = reinterpret_cast<const __half*>(&graw);
+            {
+                __half z = __float2half_rn(0.0f);
+                __half2 c0[4] = {__halves2half2(gh[0], gh[1]), __halves2half2(gh[2], z), __halves2half2(z, z), __halves2half2(z, z)};
+                *reinterpret_cast<uint4*>(go + blk8_chunk_offset(tid, 0, 16)) = *reinterpret_cast<uint4*>(c0);
+                *reinterpret_cast<uint4*>(go + blk8_chunk_offset(tid, 1, 16)) = make_uint4(0, 0, 0, 0);
+            }
+            bwd_chain<RH, 32, true>(stage, tmem_base, tmem_row, sbase, smem, Cfg::ACC_R0, Cfg::ACC_RH, Cfg::ACC_RO, L.r0, L.hr, L.g, L.go, L.wr, accumulate, tid);
+            // ---- d(density out) = d(rgb input)[0:16], + dL/dsigma on channel 0: add_density_gradient (nerf_network.h:62-74) ----
+            float dd[16];
+            tmem_ld16(tmem_row, dd); tmem_wait_ld();
+            dd[0] = __half2float(__float2half_rn(dd[0])) + __half2float(gh[3]);
+            *reinterpret_cast<uint4*>(go + blk8_chunk_offset(tid, 0, 16)) = pack8(dd, false);
+            *reinterpret_cast<uint4*>(go + blk8_chunk_offset(tid, 1, 16)) = pack8(dd + 8, false);
+        } else {
+            const uint4* gsrc = reinterpret_cast<const uint4*>(p.dL_dout + (size_t)row_g * p.dout_stride);
+            *reinterpret_cast<uint4*>(go + blk8_chunk_offset(tid, 0, 16)) = __ldg(gsrc);
+            *reinterpret_cast<uint4*>(go + blk8_chunk_offset(tid, 1, 16)) = __ldg(gsrc + 1);
+        }
+        bwd_chain<DH, PW, NEED_DENC>(stage, tmem_base, tmem_row, sbase, smem, Cfg::ACC_D0, Cfg::ACC_DH, Cfg::ACC_DO, L.x0, L.hd, L.g, L.go, L.wd, accumulate, tid);
+        // X0 is free now: prefetch the next tile's input while the last epilogue runs
+        const uint32_t next = tile + gridDim.x;
+        if (tid == 0 && next < p.n_tiles) {
+            mbar_expect_tx(bar_full, X_BYTES);
+            bulk_g2s(smem + L.x0, p.enc + (size_t)next * TILE_ROWS * PW, X_BYTES, bar_full);
+        }
+        if (NEED_DENC) {
+#pragma unroll
+            for (uint32_t j = 0; j < PW; j += 16) {
+                float v[16];
+                tmem_ld16(tmem_row + j, v); tmem_wait_ld();
+                *reinterpret_cast<uint4*>(p.dL_denc + blk8_chunk_offset(row_g, j >> 3, PW)) = pack8(v, false);
+                *reinterpret_cast<uint4*>(p.dL_denc + blk8_chunk_offset(row_g, (j >> 3) + 1, PW)) = pack8(v + 8, false);
+            }
+        }
+    }
+    // ---- flush the TMEM-resident weight gradients ----
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    if (it > 0) {
+        float* wg = p.wgrad;
+        flush_wgrad<PW, false>(tmem_row, Cfg::ACC_D0, wg, PW, tid); wg += MLP_WIDTH * PW;
+        for (uint32_t l = 1; l < DH; ++l) { flush_wgrad<64, false>(tmem_row, Cfg::ACC_DH + 64 * (l - 1), wg, 64, tid); wg += 64 * 64; }
+        flush_wgrad<16, true>(tmem_row, Cfg::ACC_DO, wg, 64, tid); wg += 16 * 64;
+        if (MODE == MODE_NERF) {
+            flush_wgrad<32, false>(tmem_row, Cfg::ACC_R0, wg, 32, tid); wg += 64 * 32;
+            for (uint32_t l = 1; l < RH; ++l) { flush_wgrad<64, false>(tmem_row, Cfg::ACC_RH + 64 * (l - 1), wg, 64, tid); wg += 64 * 64; }
+            flush_wgrad<16, true>(tmem_row, Cfg::ACC_RO, wg, 64, tid);
+        }
+    }
+    fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
+}
+
+
+// =================================================================================================================
+// Host launchers
+// =================================================================================================================
+static int sm_count() {
+    static int n = 0;
+    if (!n) { int dev; NGP_CUDA_CHECK(cudaGetDevice(&dev)); NGP_CUDA_CHECK(cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev)); }
+    return n;
+}
+
+template <class K>
+static uint32_t persistent_grid(K kernel, uint32_t smem_bytes, uint32_t n_tiles) {
+    NGP_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+    int per_sm = 0;
+    NGP_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, 128, smem_bytes));
+    NGP_CHECK(per_sm >= 1, "fused MLP kernel does not fit on an SM");
+    return std::min<uint32_t>(n_tiles, (uint32_t)per_sm * (uint32_t)sm_count());
+}
+
+template <uint32_t PW, uint32_t DH, uint32_t RH, int MODE>
+static void launch_fwd(cudaStream_t s, const FwdParams& p) {
+    const FwdSmem<PW, DH, RH, MODE> L;
+    auto k = mlp_forward_kernel<PW, DH, RH, MODE>;
+    const uint32_t grid = persistent_grid(k, L.total, p.n_tiles);
+    k<<<grid, 128, L.total, s>>>(p);
+    NGP_POST_LAUNCH();
+}
+
+template <uint32_t PW, uint32_t DH, uint32_t RH, int MODE>
+static void launch_bwd(cudaStream_t s, const BwdParams& p) {
+    const BwdCfg<PW, DH, RH, MODE> L;
+    if (p.dL_denc) {
+        auto k = mlp_backward_kernel<PW, DH, RH, MODE, true>;
+        const uint32_t grid = persistent_grid(k, L.total, p.n_tiles);
+        k<<<grid, 128, L.total, s>>>(p);
+    } else {
+        auto k = mlp_backward_kernel<PW, DH, RH, MODE, false>;
+        const uint32_t grid = persistent_grid(k, L.total, p.n_tiles);
+        k<<<grid, 128, L.total, s>>>(p);
+    }
+    NGP_POST_LAUNCH();
+}
+
+#define NERF_DISPATCH(FN, MODE, d, ...)                                                                          \
+    do {                                                                                                          \
+        const uint32_t key = (d).pos_width * 100 + (d).density_hidden * 10 + (d).rgb_hidden;                      \
+        switch (key) {                                                                                            \
+            case 1611: FN<16, 1, 1, MODE>(__VA_ARGS__); break;                                                    \
+            case 1612: FN<16, 1, 2, MODE>(__VA_ARGS__); break;                                                    \
+            case 1622: FN<16, 2, 2, MODE>(__VA_ARGS__); break;                                                    \
+            case 3211: FN<32, 1, 1, MODE>(__VA_ARGS__); break;                                                    \
+            case 3212: FN<32, 1, 2, MODE>(__VA_ARGS__); break;                                                    \
+            case 3222: FN<32, 2, 2, MODE>(__VA_ARGS__); break;                                                    \
+            default: throw Error("FullyFusedMLP: unsupported NeRF network shape (encoder width 16/32, density hidden 1-2, rgb hidden 1-2, 64 neurons)"); \
+        }                                                                                                         \
+    } while (0)
+
+#define PLAIN_DISPATCH(FN, in_w, nh, ...)                                                                        \
+    do {                                                                                                          \
+        const uint32_t key = (in_w) * 10 + (nh);                                                                  \
+        switch (key) {                                                                                            \
+            case 161: FN<16, 1, 1, MODE_PLAIN>(__VA_ARGS__); break;                                               \
+            case 162: FN<16, 2, 1, MODE_PLAIN>(__VA_ARGS__); break;                                               \
+            case 321: FN<32, 1, 1, MODE_PLAIN>(__VA_ARGS__); break;                                               \
+            case 322: FN<32, 2, 1, MODE_PLAIN>(__VA_ARGS__); break;                                               \
+            case 323: FN<32, 3, 1, MODE_PLAIN>(__VA_ARGS__); break;                                               \
+            default: throw Error("FullyFusedMLP: unsupported shape (input width 16/32, 1-3 hidden layers, 64 neurons)"); \
+        }                                                                                                         \
+    } while (0)
+
+static uint32_t tiles_of(uint32_t n) {
+    NGP_CHECK(n % TILE_ROWS == 0, "batch size must be a multiple of 128 (callers round to batch_size_granularity = 256)");
+    return n / TILE_ROWS;
+}
+
+void nerf_mlp_forward(cudaStream_t s, const NerfNetDims& d, const __half* wd, const __half* wr, const __half* enc, const float* coords,
+                      uint32_t n, __half* out) {
+    if (n == 0) return;
+    FwdParams p{wd, wr, enc, coords, out, 4, tiles_of(n)};
+    NERF_DISPATCH(launch_fwd, MODE_NERF, d, s, p);
+}
+
+void nerf_mlp_density(cudaStream_t s, const NerfNetDims& d, const __half* wd, const __half* enc, uint32_t n, __half* out) {
+    if (n == 0) return;
+    FwdParams p{wd, nullptr, enc, nullptr, out, 1, tiles_of(n)};
+    NerfNetDims dd = d; dd.rgb_hidden = 1;
+    NERF_DISPATCH(launch_fwd, MODE_DENSITY, dd, s, p);
+}
+
+void nerf_mlp_backward(cudaStream_t s, const NerfNetDims& d, const __half* wd, const __half* wr, const __half* enc, const float* coords,
+                       uint32_t n, const __half* dL_dout, __half* dL_denc, float* wgrad) {
+    if (n == 0) return;
+    BwdParams p{wd, wr, enc, coords, dL_dout, 4, dL_denc, wgrad, tiles_of(n)};
+    NERF_DISPATCH(launch_bwd, MODE_NERF, d, s, p);
+}
+
+void mlp_forward(cudaStream_t s, uint32_t in_w, uint32_t nh, const __half* w, const __half* in, uint32_t n, __half* out, uint32_t out_stride) {
+    if (n == 0) return;
+    NGP_CHECK(out_stride % 8 == 0 && out_stride >= 16, "mlp_forward: out_stride must be a multiple of 8 and >= 16");
+    FwdParams p{w, nullptr, in, nullptr, out, out_stride, tiles_of(n)};
+    PLAIN_DISPATCH(launch_fwd, in_w, nh, s, p);
+}
+
+void mlp_backward(cudaStream_t s, uint32_t in_w, uint32_t nh, const __half* w, const __half* in, uint32_t n, const __half* dL_dout,
+                  uint32_t dout_stride, __half* dL_din, float* wgrad) {
+    if (n == 0) return;
+    NGP_CHECK(dout_stride % 8 == 0 && dout_stride >= 16, "mlp_backward: dout_stride must be a multiple of 8 and >= 16");
+    BwdParams p{w, nullptr, in, nullptr, dL_dout, dout_stride, dL_din, wgrad, tiles_of(n)};
+    PLAIN_DISPATCH(launch_bwd, in_w, nh, s, p);
+}
+
+}  // namespace ngp

@@ -1,0 +1,209 @@
+// Host-side model objects (see network.h).  Parameter layout follows NerfNetwork::set_params_impl
+// (nerf_network.h:430-457): [density MLP | rgb MLP | position encoding | direction encoding (0 params)].
+#include "network.h"
+#include <cmath>
+#include <cstring>
+
+namespace ngp {
+
+MlpConfig parse_mlp_config(const Json& j, const char* what) {
+    MlpConfig c;
+    const std::string otype = to_lower(j.value("otype", "FullyFusedMLP"));
+    NGP_CHECK(otype == "fullyfusedmlp" || otype == "megakernelmlp", std::string(what) + ": only otype FullyFusedMLP is implemented on this path (got '" + otype + "')");
+    NGP_CHECK(to_lower(j.value("activation", "ReLU")) == "relu", std::string(what) + ": only ReLU hidden activation is implemented");
+    NGP_CHECK(to_lower(j.value("output_activation", "None")) == "none", std::string(what) + ": only output_activation None is implemented");
+    c.n_neurons = (uint32_t)j.value("n_neurons", 64.0);
+    c.n_hidden_layers = (uint32_t)j.value("n_hidden_layers", 2.0);
+    c.n_output_dims = (uint32_t)j.value("n_output_dims", 16.0);
+    NGP_CHECK(c.n_neurons == 64, std::string(what) + ": n_neurons must be 64 on the tcgen05 path");
+    NGP_CHECK(c.n_hidden_layers >= 1 && c.n_hidden_layers <= 3, std::string(what) + ": n_hidden_layers must be 1..3");
+    return c;
+}
+
+// encoding config derivation: testbed.cu:3961-4005 (fork: per_level_scale is never injected -> tcnn default 2.0)
+void grid_from_json(GridLayout& g, const Json& enc, uint32_t n_pos_dims) {
+    const std::string otype = to_lower(enc.value("otype", "HashGrid"));
+    NGP_CHECK(otype.find("grid") != std::string::npos && otype != "densegrid" && otype != "tiledgrid",
+              "encoding: only otype HashGrid is implemented on this path (got '" + otype + "')");
+    const uint32_t F = (uint32_t)enc.value("n_features_per_level", 2.0);
+    uint32_t L = (uint32_t)enc.value("n_levels", 16.0);
+    if (enc.contains("n_features") && enc.value("n_features", 0.0) > 0) L = (uint32_t)enc.value("n_features", 0.0) / F;
+    const uint32_t log2T = (uint32_t)enc.value("log2_hashmap_size", 19.0);
+    uint32_t base = (uint32_t)enc.value("base_resolution", 0.0);
+    if (!base) base = 1u << ((uint32_t)enc.value("log2_hashmap_size", 15.0) / n_pos_dims);
+    const float b = (float)enc.value("per_level_scale", 2.0);
+    grid_make_layout(g, n_pos_dims, L, F, log2T, base, b);
+}
+
+void mlp_init_host(uint32_t in_w, uint32_t n_hidden, Pcg32& rng, float* p) {
+    uint32_t cw = in_w;
+    for (uint32_t l = 0; l <= n_hidden; ++l) {
+        const uint32_t rows = (l == n_hidden) ? MLP_OUT_PAD : MLP_WIDTH;
+        const float s = sqrtf(6.0f / (float)(rows + cw));
+        for (uint32_t i = 0; i < rows * cw; ++i) *p++ = (rng.next_float() * 2.0f - 1.0f) * s;
+        cw = MLP_WIDTH;
+    }
+}
+
+static void check_dir_encoding(const Json& cfg) {
+    if (!cfg.contains("dir_encoding")) return;   // reference default is the SH composite as well
+    const Json& d = cfg.at("dir_encoding");
+    const Json* sh = &d;
+    if (to_lower(d.value("otype", "")) == "composite") {
+        NGP_CHECK(d.contains("nested") && !d.at("nested").arr.empty(), "dir_encoding: Composite needs nested encodings");
+        sh = &d.at("nested").arr[0];
+        for (size_t i = 1; i < d.at("nested").arr.size(); ++i)
+            NGP_CHECK(to_lower(d.at("nested").arr[i].value("otype", "")) == "identity", "dir_encoding: nested[1..] must be Identity");
+    }
+    NGP_CHECK(to_lower(sh->value("otype", "")) == "sphericalharmonics" && (int)sh->value("degree", 4.0) == 4,
+              "dir_encoding: only SphericalHarmonics degree 4 (+Identity) is implemented on this path");
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+NerfNetwork::NerfNetwork(const Json& cfg) {
+    NGP_CHECK(cfg.contains("encoding") && cfg.contains("network"), "network config needs 'encoding' and 'network'");
+    grid_from_json(grid, cfg.at("encoding"), 3);
+    check_dir_encoding(cfg);
+    MlpConfig dn = parse_mlp_config(cfg.at("network"), "network");
+    MlpConfig rn = parse_mlp_config(cfg.contains("rgb_network") ? cfg.at("rgb_network") : cfg.at("network"), "rgb_network");
+    NGP_CHECK(!cfg.at("network").contains("n_output_dims") || dn.n_output_dims == 16, "network.n_output_dims must be 16");
+    NGP_CHECK(dn.n_hidden_layers <= 2 && rn.n_hidden_layers <= 2, "NeRF path: density/rgb networks support 1..2 hidden layers");
+    dims.pos_width = grid.padded_width;
+    NGP_CHECK(dims.pos_width == 16 || dims.pos_width == 32, "NeRF path: n_levels*n_features_per_level must pad to 16 or 32");
+    dims.density_hidden = dn.n_hidden_layers; dims.rgb_hidden = rn.n_hidden_layers;
+    const uint64_t nd = mlp_n_params(dims.pos_width, dims.density_hidden), nr = mlp_n_params(32, dims.rgb_hidden);
+    off_density = 0; off_rgb = nd; off_grid = nd + nr;
+    n_matrix_params = nd + nr;
+    n_params = n_matrix_params + grid.n_params;
+}
+
+void NerfNetwork::initialize_params(uint64_t seed, float* master_dev, cudaStream_t s) {
+    // initialize_params order (nerf_network.h:445-457): density MLP, rgb MLP, pos encoding; seed testbed.h:609
+    Pcg32 rng(seed);
+    std::vector<float> host(n_matrix_params);
+    mlp_init_host(dims.pos_width, dims.density_hidden, rng, host.data() + off_density);
+    mlp_init_host(32, dims.rgb_hidden, rng, host.data() + off_rgb);
+    NGP_CUDA_CHECK(cudaMemcpyAsync(master_dev, host.data(), host.size() * sizeof(float), cudaMemcpyHostToDevice, s));
+    NGP_CUDA_CHECK(cudaStreamSynchronize(s));
+    grid_init(s, grid, rng, master_dev + off_grid);
+}
+
+void NerfNetwork::inference(cudaStream_t s, const __half* params, const float* coords, uint32_t n, __half* out) {
+    __half* enc = enc_buf.get<__half>((size_t)n * dims.pos_width);
+    grid_forward(s, grid, params + off_grid, coords, 7, n, enc, LAYOUT_BLK8);
+    nerf_mlp_forward(s, dims, params + off_density, params + off_rgb, enc, coords, n, out);
+}
+
+void NerfNetwork::density(cudaStream_t s, const __half* params, const float* pos, uint32_t pos_stride, uint32_t n, __half* out) {
+    __half* enc = enc_buf.get<__half>((size_t)n * dims.pos_width);
+    grid_forward(s, grid, params + off_grid, pos, pos_stride, n, enc, LAYOUT_BLK8);
+    nerf_mlp_density(s, dims, params + off_density, enc, n, out);
+}
+
+void NerfNetwork::forward_backward(cudaStream_t s, const __half* params, const float* coords, uint32_t n, const __half* dL_dout, __half* grads) {
+    __half* enc = enc_buf.get<__half>((size_t)n * dims.pos_width);
+    __half* denc = denc_buf.get<__half>((size_t)n * dims.pos_width);
+    float* wg = wgrad_buf.get<float>(n_matrix_params);
+    NGP_CUDA_CHECK(cudaMemsetAsync(wg, 0, n_matrix_params * sizeof(float), s));
+    NGP_CUDA_CHECK(cudaMemsetAsync(grads + off_grid, 0, grid.n_params * sizeof(__half), s));
+    grid_forward(s, grid, params + off_grid, coords, 7, n, enc, LAYOUT_BLK8);
+    nerf_mlp_backward(s, dims, params + off_density, params + off_rgb, enc, coords, n, dL_dout, denc, wg);
+    cast_f32_to_half(s, wg, grads, n_matrix_params);
+    grid_backward(s, grid, coords, 7, n, denc, LAYOUT_BLK8, grads + off_grid);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+EncodedMlp::EncodedMlp(const Json& cfg, uint32_t n_pos_dims, uint32_t n_output_dims) {
+    NGP_CHECK(cfg.contains("encoding") && cfg.contains("network"), "network config needs 'encoding' and 'network'");
+    grid_from_json(grid, cfg.at("encoding"), n_pos_dims);
+    MlpConfig mc = parse_mlp_config(cfg.at("network"), "network");
+    NGP_CHECK(grid.padded_width == 16 || grid.padded_width == 32, "n_levels*n_features_per_level must pad to 16 or 32");
+    NGP_CHECK(n_output_dims <= 16, "n_output_dims must be <= 16");
+    n_hidden = mc.n_hidden_layers; n_output = n_output_dims;
+    off_mlp = 0; n_matrix_params = mlp_n_params(grid.padded_width, n_hidden); off_grid = n_matrix_params;
+    n_params = n_matrix_params + grid.n_params;
+}
+
+void EncodedMlp::initialize_params(uint64_t seed, float* master_dev, cudaStream_t s) {
+    Pcg32 rng(seed);
+    std::vector<float> host(n_matrix_params);
+    mlp_init_host(grid.padded_width, n_hidden, rng, host.data());
+    NGP_CUDA_CHECK(cudaMemcpyAsync(master_dev, host.data(), host.size() * sizeof(float), cudaMemcpyHostToDevice, s));
+    NGP_CUDA_CHECK(cudaStreamSynchronize(s));
+    grid_init(s, grid, rng, master_dev + off_grid);
+}
+
+void EncodedMlp::inference(cudaStream_t s, const __half* params, const float* x, uint32_t x_stride, uint32_t n, __half* out) {
+    __half* enc = enc_buf.get<__half>((size_t)n * grid.padded_width);
+    grid_forward(s, grid, params + off_grid, x, x_stride, n, enc, LAYOUT_BLK8);
+    mlp_forward(s, grid.padded_width, n_hidden, params + off_mlp, enc, n, out, 16);
+}
+
+void EncodedMlp::forward_backward(cudaStream_t s, const __half* params, const float* x, uint32_t x_stride, uint32_t n, const __half* dL_dout, __half* grads) {
+    __half* enc = enc_buf.get<__half>((size_t)n * grid.padded_width);
+    __half* denc = denc_buf.get<__half>((size_t)n * grid.padded_width);
+    float* wg = wgrad_buf.get<float>(n_matrix_params);
+    NGP_CUDA_CHECK(cudaMemsetAsync(wg, 0, n_matrix_params * sizeof(float), s));
+    NGP_CUDA_CHECK(cudaMemsetAsync(grads + off_grid, 0, grid.n_params * sizeof(__half), s));
+    grid_forward(s, grid, params + off_grid, x, x_stride, n, enc, LAYOUT_BLK8);
+    mlp_backward(s, grid.padded_width, n_hidden, params + off_mlp, enc, n, dL_dout, 16, denc, wg);
+    cast_f32_to_half(s, wg, grads, n_matrix_params);
+    grid_backward(s, grid, x, x_stride, n, denc, LAYOUT_BLK8, grads + off_grid);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+Optimizer::Optimizer(const Json& j) { update_hyperparams(j); current_lr = learning_rate; }
+
+void Optimizer::update_hyperparams(const Json& j) {
+    const Json* cur = &j;
+    for (int depth = 0; depth < 8; ++depth) {
+        const std::string otype = to_lower(cur->value("otype", "Adam"));
+        if (otype == "ema") ema_decay = (float)cur->value("decay", 0.99);
+        else if (otype == "exponentialdecay") {
+            decay_start = (uint32_t)cur->value("decay_start", 0.0); decay_interval = (uint32_t)cur->value("decay_interval", 0.0);
+            decay_base = (float)cur->value("decay_base", 1.0);
+            decay_end = cur->contains("decay_end") ? (uint32_t)cur->value("decay_end", 0.0) : 0xFFFFFFFFu;
+        } else if (otype == "adam") {
+            learning_rate = (float)cur->value("learning_rate", 1e-3); beta1 = (float)cur->value("beta1", 0.9); beta2 = (float)cur->value("beta2", 0.999);
+            epsilon = (float)cur->value("epsilon", 1e-8); l2_reg = (float)cur->value("l2_reg", 1e-8);
+            optimize_matrix = cur->value("optimize_matrix_params", true); optimize_non_matrix = cur->value("optimize_non_matrix_params", true);
+        } else throw Error("optimizer: unsupported otype '" + otype + "' (Ema / ExponentialDecay / Adam are implemented)");
+        if (!cur->contains("nested")) break;
+        cur = &cur->at("nested");
+    }
+}
+
+Trainer::Trainer(uint64_t n, uint64_t n_matrix, const Json& optimizer_cfg) : n_params(n), n_matrix_params(n_matrix), opt(optimizer_cfg) {
+    NGP_CUDA_CHECK(cudaMalloc(&master, n * 4)); NGP_CUDA_CHECK(cudaMalloc(&params, n * 2)); NGP_CUDA_CHECK(cudaMalloc(&grads, n * 2));
+    NGP_CUDA_CHECK(cudaMalloc(&m, n * 4)); NGP_CUDA_CHECK(cudaMalloc(&v, n * 4)); NGP_CUDA_CHECK(cudaMalloc(&steps, n * 4));
+    NGP_CUDA_CHECK(cudaMemset(m, 0, n * 4)); NGP_CUDA_CHECK(cudaMemset(v, 0, n * 4)); NGP_CUDA_CHECK(cudaMemset(steps, 0, n * 4));
+    NGP_CUDA_CHECK(cudaMemset(grads, 0, n * 2));
+    if (opt.ema_decay > 0.0f) {
+        NGP_CUDA_CHECK(cudaMalloc(&ema, n * 4)); NGP_CUDA_CHECK(cudaMemset(ema, 0, n * 4));
+        NGP_CUDA_CHECK(cudaMalloc(&inference_params, n * 2));
+    } else inference_params = params;
+}
+
+Trainer::~Trainer() {
+    if (inference_params && inference_params != params) cudaFree(inference_params);
+    cudaFree(master); cudaFree(params); cudaFree(grads); cudaFree(m); cudaFree(v); cudaFree(steps); if (ema) cudaFree(ema);
+}
+
+void Trainer::params_from_master(cudaStream_t s) {
+    cast_f32_to_half(s, master, params, n_params);
+    if (inference_params != params) NGP_CUDA_CHECK(cudaMemcpyAsync(inference_params, params, n_params * 2, cudaMemcpyDeviceToDevice, s));
+}
+
+void Trainer::optimizer_step(cudaStream_t s, float loss_scale) {
+    AdamHyper h{};
+    h.learning_rate = opt.current_lr; h.beta1 = opt.beta1; h.beta2 = opt.beta2; h.epsilon = opt.epsilon; h.l2_reg = opt.l2_reg;
+    h.loss_scale = loss_scale; h.n_matrix_params = n_matrix_params;
+    h.optimize_matrix = opt.optimize_matrix; h.optimize_non_matrix = opt.optimize_non_matrix;
+    h.ema_decay = opt.ema_decay; h.ema_step = opt.step_count + 1;
+    adam_step(s, h, n_params, master, params, grads, m, v, steps, ema, ema ? inference_params : nullptr);
+    ++opt.step_count;
+    const uint32_t sc = opt.step_count;
+    if (opt.decay_interval > 0 && sc >= opt.decay_start && sc < opt.decay_end && (sc - opt.decay_start) % opt.decay_interval == 0) opt.current_lr *= opt.decay_base;
+}
+
+}  // namespace ngp

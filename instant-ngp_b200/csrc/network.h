@@ -1,0 +1,86 @@
+// Host-side model objects mirroring the reference's operator surface:
+//   HashGridEncoding      <-> tcnn::create_encoding<T>(n_dims, json, alignment)        (nerf_network.h:93-95, testbed.cu:4101)
+//   NerfNetwork           <-> ngp::NerfNetwork<T>                                       (nerf_network.h:76-578)
+//   EncodedMlp            <-> tcnn::NetworkWithInputEncoding<T>                         (testbed.cu:4110; image / SDF modes)
+//   Optimizer             <-> tcnn::create_optimizer(json): Ema(ExponentialDecay(Adam)) (testbed.cu:4008, configs/nerf/base.json:5-22)
+//   Trainer               <-> tcnn::Trainer<float,T,T> (owns master/params/inference params/gradients)  (testbed.cu:4129)
+#pragma once
+#include "ngp_internal.h"
+#include "json_mini.h"
+#include <vector>
+
+namespace ngp {
+
+// grow-only device scratch (stands in for tcnn::GPUMemoryArena allocations tied to a stream)
+struct DeviceBuffer {
+    void* ptr = nullptr; size_t bytes = 0;
+    DeviceBuffer() = default;
+    DeviceBuffer(const DeviceBuffer&) = delete;
+    DeviceBuffer& operator=(const DeviceBuffer&) = delete;
+    ~DeviceBuffer() { if (ptr) cudaFree(ptr); }
+    template <class T> T* get(size_t count) {
+        size_t need = count * sizeof(T);
+        if (need > bytes) { if (ptr) NGP_CUDA_CHECK(cudaFree(ptr)); ptr = nullptr; bytes = 0; size_t cap = need + need / 4 + 256; NGP_CUDA_CHECK(cudaMalloc(&ptr, cap)); bytes = cap; }
+        return reinterpret_cast<T*>(ptr);
+    }
+    template <class T> T* as() const { return reinterpret_cast<T*>(ptr); }
+};
+
+struct MlpConfig { uint32_t n_neurons = 64, n_hidden_layers = 2, n_output_dims = 16; };
+MlpConfig parse_mlp_config(const Json& j, const char* what);
+void grid_from_json(GridLayout& g, const Json& enc, uint32_t n_pos_dims);
+void mlp_init_host(uint32_t in_w, uint32_t n_hidden, Pcg32& rng, float* params);   // Xavier uniform, memory order
+
+struct NerfNetwork {
+    GridLayout grid; NerfNetDims dims;
+    uint64_t off_density = 0, off_rgb = 0, off_grid = 0, n_params = 0, n_matrix_params = 0;
+    DeviceBuffer enc_buf, denc_buf, wgrad_buf;
+
+    // config = the reference's network JSON ("encoding", "network", "dir_encoding", "rgb_network")
+    explicit NerfNetwork(const Json& config);
+    void initialize_params(uint64_t seed, float* master_dev, cudaStream_t s);
+    // coords [n][7] fp32; out [n][4] fp16 ; n % 128 == 0
+    void inference(cudaStream_t s, const __half* params, const float* coords, uint32_t n, __half* out);
+    // pos [n][pos_stride] fp32; out [n] fp16 (raw density)
+    void density(cudaStream_t s, const __half* params, const float* pos, uint32_t pos_stride, uint32_t n, __half* out);
+    // forward(recompute)+backward; grads: param-shaped fp16, OVERWRITTEN (EGradientMode::Overwrite, testbed_nerf.cu:4078)
+    void forward_backward(cudaStream_t s, const __half* params, const float* coords, uint32_t n, const __half* dL_dout, __half* grads);
+};
+
+struct EncodedMlp {
+    GridLayout grid; uint32_t n_hidden = 2, n_output = 3;
+    uint64_t off_mlp = 0, off_grid = 0, n_params = 0, n_matrix_params = 0;
+    DeviceBuffer enc_buf, denc_buf, wgrad_buf;
+    EncodedMlp(const Json& config, uint32_t n_pos_dims, uint32_t n_output_dims);
+    void initialize_params(uint64_t seed, float* master_dev, cudaStream_t s);
+    // x [n][x_stride] fp32; out [n][16] fp16
+    void inference(cudaStream_t s, const __half* params, const float* x, uint32_t x_stride, uint32_t n, __half* out);
+    void forward_backward(cudaStream_t s, const __half* params, const float* x, uint32_t x_stride, uint32_t n, const __half* dL_dout, __half* grads);
+};
+
+struct Optimizer {
+    // Adam leaf
+    float learning_rate = 1e-2f, beta1 = 0.9f, beta2 = 0.99f, epsilon = 1e-15f, l2_reg = 1e-6f;
+    bool optimize_matrix = true, optimize_non_matrix = true;
+    // ExponentialDecay
+    uint32_t decay_start = 0, decay_interval = 0, decay_end = 0xFFFFFFFFu; float decay_base = 1.0f;
+    // Ema
+    float ema_decay = 0.0f;
+    uint32_t step_count = 0; float current_lr = 1e-2f;
+    explicit Optimizer(const Json& j);
+    void update_hyperparams(const Json& j);   // testbed.cu:4339-4346
+};
+
+struct Trainer {
+    uint64_t n_params = 0, n_matrix_params = 0;
+    float* master = nullptr; __half* params = nullptr; __half* inference_params = nullptr; __half* grads = nullptr;
+    float* m = nullptr; float* v = nullptr; uint32_t* steps = nullptr; float* ema = nullptr;
+    Optimizer opt;
+    Trainer(uint64_t n_params, uint64_t n_matrix, const Json& optimizer_cfg);
+    ~Trainer();
+    Trainer(const Trainer&) = delete;
+    void params_from_master(cudaStream_t s);             // fp16 copies after initialize_params
+    void optimizer_step(cudaStream_t s, float loss_scale);
+};
+
+}  // namespace ngp

@@ -8,6 +8,7 @@
 #include <stdint.h>
 #include <stdexcept>
 #include <string>
+#include <atomic>
 
 #define NGP_HD __host__ __device__ __forceinline__
 #define NGP_D __device__ __forceinline__
@@ -27,6 +28,14 @@ struct Error : std::runtime_error { using std::runtime_error::runtime_error; };
 #define NGP_CHECK(cond, msg)                                                                  \
     do {                                                                                       \
         if (!(cond)) throw ngp::Error(std::string(__FILE__) + ":" + std::to_string(__LINE__) + " " + (msg)); \
+    } while (0)
+
+// every kernel launch of this library goes through NGP_POST_LAUNCH(): error check + launch counter (ngp_kernel_launch_count)
+extern std::atomic<uint64_t> g_launch_count;
+#define NGP_POST_LAUNCH()                        \
+    do {                                         \
+        NGP_CUDA_CHECK(cudaGetLastError());      \
+        ngp::g_launch_count.fetch_add(1, std::memory_order_relaxed); \
     } while (0)
 
 constexpr uint32_t BATCH_GRANULARITY = 256;   // tcnn::batch_size_granularity as used by the reference callers
