@@ -1,0 +1,219 @@
+"""ORACLE — TEST INFRASTRUCTURE ONLY.  ctypes/numpy front-end of oracle/libngp_ref.so (see oracle/ngp_ref.h).
+
+May be imported only by tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+u32, u64, i32, f32, vp = C.c_uint32, C.c_uint64, C.c_int, C.c_float, C.c_void_p
+
+
+class GridCfg(C.Structure):
+    _fields_ = [("n_dims", u32), ("n_levels", u32), ("n_features", u32), ("log2_hashmap_size", u32), ("base_resolution", u32),
+                ("per_level_scale", f32)]
+
+
+class NerfNetCfg(C.Structure):
+    _fields_ = [("grid", GridCfg), ("width", u32), ("density_hidden", u32), ("rgb_hidden", u32)]
+
+
+class AdamCfg(C.Structure):
+    _fields_ = [("learning_rate", f32), ("beta1", f32), ("beta2", f32), ("epsilon", f32), ("l2_reg", f32), ("loss_scale", f32),
+                ("n_matrix_params", u64), ("optimize_matrix", i32), ("optimize_non_matrix", i32)]
+
+
+class Image(C.Structure):
+    _fields_ = [("pixels", vp), ("data_type", C.c_int32), ("lens_mode", C.c_int32), ("lens_params", f32 * 4), ("res", C.c_int32 * 2),
+                ("principal_point", f32 * 2), ("focal_length", f32 * 2), ("xform", f32 * 12)]
+
+
+class Aabb(C.Structure):
+    _fields_ = [("min", f32 * 3), ("max", f32 * 3)]
+
+
+class SamplerOut(C.Structure):
+    _fields_ = [("ray_indices", vp), ("rays", vp), ("numsteps", vp), ("coords", vp), ("ray_counter", u32), ("numsteps_counter", u32)]
+
+
+class LossCfg(C.Structure):
+    _fields_ = [("loss_type", i32), ("rgb_activation", i32), ("density_activation", i32), ("random_bg_color", i32), ("linear_colors", i32),
+                ("snap_to_pixel_centers", i32), ("background_color", f32 * 3), ("loss_scale", f32), ("near_distance", f32), ("mean_density", f32)]
+
+
+class LossOut(C.Structure):
+    _fields_ = [("dloss_doutput", vp), ("coords_compacted", vp), ("loss", vp), ("numsteps", vp), ("rgb_ray", vp), ("compacted_counter", u32)]
+
+
+class RenderCfg(C.Structure):
+    _fields_ = [("res", C.c_int32 * 2), ("focal_length", f32 * 2), ("screen_center", f32 * 2), ("camera", f32 * 12), ("render_aabb", Aabb),
+                ("train_aabb", Aabb), ("cone_angle_constant", f32), ("min_transmittance", f32), ("max_mip", u32), ("spp_index", u32),
+                ("snap_to_pixel_centers", i32), ("rgb_activation", i32), ("density_activation", i32), ("linear_colors", i32),
+                ("y0", C.c_int32), ("y1", C.c_int32)]
+
+
+def build():
+    subprocess.check_call(["make", "-s", "-C", _HERE, "libngp_ref.so"])
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        path = os.path.join(_HERE, "libngp_ref.so")
+        if not os.path.exists(path):
+            build()
+        _LIB = C.CDLL(path)
+        l = _LIB
+        l.ref_grid_layout.restype = u64
+        l.ref_nerf_n_params.restype = u64
+        l.ref_nerf_pos_width.restype = u32
+        l.ref_mlp_n_params.restype = u32
+        l.ref_exp_decay_lr.restype = f32
+        l.ref_exp_decay_lr.argtypes = [f32, u32, u32, u32, f32, u32]
+        l.ref_update_bitfield.restype = f32
+        l.ref_l2_loss.restype = C.c_double
+        l.ref_l2_loss.argtypes = [vp, u32, vp, u32, f32, vp]
+        l.ref_next_rays_per_batch.restype = u32
+        for name in ["ref_to_stepping_space", "ref_from_stepping_space", "ref_calc_dt", "ref_srgb_to_linear", "ref_linear_to_srgb"]:
+            getattr(l, name).restype = f32
+        l.ref_to_stepping_space.argtypes = [f32, f32]; l.ref_from_stepping_space.argtypes = [f32, f32]; l.ref_calc_dt.argtypes = [f32, f32]
+        l.ref_advance_n_steps.restype = f32; l.ref_advance_n_steps.argtypes = [f32, f32, f32]
+        l.ref_srgb_to_linear.argtypes = [f32]; l.ref_linear_to_srgb.argtypes = [f32]
+        l.ref_ld_random_val.restype = f32; l.ref_ld_random_val.argtypes = [u32, u32]
+        l.ref_mip_from_dt.argtypes = [f32, vp, u32]
+        l.ref_ema_grid_samples.argtypes = [u32, f32, vp, vp]
+        l.ref_generate_grid_samples_nonuniform.argtypes = [u32, u64, u64, u32, vp, vp, vp, vp, u32, f32]
+        l.ref_ema_step.argtypes = [u64, f32, u32, vp, vp, vp]
+        l.ref_generate_training_samples.argtypes = [u32, vp, u32, u32, u64, u64, u32, vp, vp, u32, i32, f32, vp]
+    return _LIB
+
+
+def P(a):
+    """numpy array -> void*"""
+    return a.ctypes.data_as(vp) if a is not None else vp(0)
+
+
+def grid_cfg(n_dims=3, n_levels=16, n_features=2, log2_hashmap_size=19, base_resolution=16, per_level_scale=2.0):
+    return GridCfg(n_dims, n_levels, n_features, log2_hashmap_size, base_resolution, per_level_scale)
+
+
+def grid_cfg_from_json(enc, n_dims):
+    F = int(enc.get("n_features_per_level", 2))
+    L = int(enc.get("n_levels", 16))
+    log2T = int(enc.get("log2_hashmap_size", 19))
+    base = int(enc.get("base_resolution", 0)) or (1 << (int(enc.get("log2_hashmap_size", 15)) // n_dims))
+    return grid_cfg(n_dims, L, F, log2T, base, float(enc.get("per_level_scale", 2.0)))
+
+
+def nerf_cfg_from_json(cfg):
+    return NerfNetCfg(grid_cfg_from_json(cfg["encoding"], 3), 64, int(cfg["network"].get("n_hidden_layers", 1)),
+                      int(cfg.get("rgb_network", cfg["network"]).get("n_hidden_layers", 2)))
+
+
+def grid_layout(cfg):
+    L = cfg.n_levels
+    off = np.zeros(L + 1, np.uint32); sc = np.zeros(L, np.float32); res = np.zeros(L, np.uint32)
+    n = lib().ref_grid_layout(C.byref(cfg), P(off), P(sc), P(res))
+    return int(n), off, sc, res
+
+
+def grid_corners(cfg, x, level):
+    n = x.shape[0]; k = 1 << cfg.n_dims
+    idx = np.zeros((n, k), np.uint32); w = np.zeros((n, k), np.float32)
+    lib().ref_grid_corners(C.byref(cfg), P(x), u32(x.shape[1]), u32(n), u32(level), P(idx), P(w))
+    return idx, w
+
+
+def grid_forward(cfg, table_h, x, width):
+    n = x.shape[0]
+    y = np.zeros((n, width), np.float16)
+    lib().ref_grid_forward(C.byref(cfg), P(table_h), P(x), u32(x.shape[1]), u32(n), P(y), u32(width), u32(width))
+    return y
+
+
+def grid_backward(cfg, x, dy, n_params):
+    g = np.zeros(n_params, np.float64)
+    lib().ref_grid_backward(C.byref(cfg), P(x), u32(x.shape[1]), u32(x.shape[0]), P(dy), u32(dy.shape[1]), P(g))
+    return g
+
+
+def grid_backward_input(cfg, table_h, x, dy):
+    dx = np.zeros((x.shape[0], cfg.n_dims), np.float32)
+    lib().ref_grid_backward_input(C.byref(cfg), P(table_h), P(x), u32(x.shape[1]), u32(x.shape[0]), P(dy), u32(dy.shape[1]), P(dx))
+    return dx
+
+
+def mlp_forward(w_h, in_w, n_hidden, x_h, want_acts=False):
+    n = x_h.shape[0]
+    out = np.zeros((n, 16), np.float16)
+    acts = np.zeros((n_hidden, n, 64), np.float16) if want_acts else None
+    lib().ref_mlp_forward(P(w_h), u32(in_w), u32(64), u32(n_hidden), u32(16), P(x_h), u32(x_h.shape[1]), u32(n), P(out), u32(16), P(acts))
+    return (out, acts) if want_acts else out
+
+
+def mlp_backward(w_h, in_w, n_hidden, x_h, acts, dout_h):
+    n = x_h.shape[0]
+    din = np.zeros((n, in_w), np.float16)
+    wg = np.zeros(int(lib().ref_mlp_n_params(u32(in_w), u32(64), u32(n_hidden), u32(16))), np.float64)
+    lib().ref_mlp_backward(P(w_h), u32(in_w), u32(64), u32(n_hidden), u32(16), P(x_h), u32(x_h.shape[1]), u32(n), P(acts), P(dout_h),
+                           u32(dout_h.shape[1]), P(din), u32(in_w), P(wg))
+    return din, wg
+
+
+def nerf_n_params(cfg):
+    a, b, c = u64(), u64(), u64()
+    n = lib().ref_nerf_n_params(C.byref(cfg), C.byref(a), C.byref(b), C.byref(c))
+    return int(n), a.value, b.value, c.value
+
+
+def nerf_init(cfg, seed=1337):
+    p = np.zeros(nerf_n_params(cfg)[0], np.float32)
+    lib().ref_nerf_init(C.byref(cfg), u64(seed), P(p))
+    return p
+
+
+def nerf_forward(cfg, params_h, coords):
+    out = np.zeros((coords.shape[0], 4), np.float16)
+    lib().ref_nerf_forward(C.byref(cfg), P(params_h), P(coords), u32(coords.shape[0]), P(out))
+    return out
+
+
+def nerf_density(cfg, params_h, pos):
+    out = np.zeros(pos.shape[0], np.float16)
+    lib().ref_nerf_density(C.byref(cfg), P(params_h), P(pos), u32(pos.shape[1]), u32(pos.shape[0]), P(out))
+    return out
+
+
+def nerf_backward(cfg, params_h, coords, dL_h):
+    g = np.zeros(nerf_n_params(cfg)[0], np.float64)
+    lib().ref_nerf_backward(C.byref(cfg), P(params_h), P(coords), u32(coords.shape[0]), P(dL_h), P(g))
+    return g
+
+
+def pcg32_floats(seed, skip, n):
+    out = np.zeros(n, np.float32)
+    lib().ref_pcg32_fill_float(u64(seed), u64(skip), P(out), C.c_size_t(n))
+    return out
+
+
+def adam_step(cfg, master, params_h, grads_h, m, v, steps):
+    lib().ref_adam_step(C.byref(cfg), u64(master.size), P(master), P(params_h), P(grads_h), P(m), P(v), P(steps))
+
+
+def make_image(pixels, data_type, res, focal, xform, principal=(0.5, 0.5), lens_mode=0, lens_params=(0, 0, 0, 0)):
+    im = Image()
+    im.pixels = pixels.ctypes.data
+    im.data_type = data_type; im.lens_mode = lens_mode
+    im.lens_params = (f32 * 4)(*lens_params); im.res = (C.c_int32 * 2)(*res)
+    im.principal_point = (f32 * 2)(*principal); im.focal_length = (f32 * 2)(*focal)
+    im.xform = (f32 * 12)(*[float(v) for v in np.asarray(xform, np.float32).reshape(-1)])
+    return im
+
+
+def make_aabb(lo, hi):
+    a = Aabb(); a.min = (f32 * 3)(*lo); a.max = (f32 * 3)(*hi); return a

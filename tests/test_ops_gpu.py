@@ -1,0 +1,234 @@
+"""GPU parity tests (pytest -m gpu): CUDA kernels through the C ABI vs the CPU oracle on the same seeded inputs.
+Bars (BASELINE.json north_star): hash indices bit-exact; encoding outputs <= 1e-3 relative; MLP outputs <= 2e-3."""
+import numpy as np
+import pytest
+import torch
+
+from .conftest import NERF_CFG_16x2, NERF_CFG_FORK
+
+pytestmark = pytest.mark.gpu
+
+ENC_TOL = 1e-3     # relative, fp16 tables
+MLP_TOL = 2e-3
+
+
+def _cuda(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+GRID_CASES = [
+    # (n_dims, L, F, log2T, base, b)
+    (3, 16, 2, 19, 16, 1.3819),   # BASELINE config 1
+    (3, 16, 2, 19, 16, 2.0),      # fork-effective per_level_scale (incl. the res=2^19 wrap-around level)
+    (3, 4, 4, 19, 16, 2.0),       # fork configs/nerf/base.json
+    (2, 16, 2, 15, 16, 1.5),      # image mode, 2-D
+    (3, 8, 1, 12, 4, 1.7),
+    (3, 2, 8, 14, 32, 2.0),
+]
+
+
+def _grid(ops, ref, case):
+    D, L, F, T, base, b = case
+    enc = ops.Encoding({"otype": "HashGrid", "n_levels": L, "n_features_per_level": F, "log2_hashmap_size": T, "base_resolution": base,
+                        "per_level_scale": b}, D)
+    cfg = ref.grid_cfg(D, L, F, T, base, b)
+    return enc, cfg
+
+
+@pytest.mark.parametrize("case", GRID_CASES)
+def test_grid_level_table_and_indices_bit_exact(ops, ref, case):
+    enc, cfg = _grid(ops, ref, case)
+    n_params, off, sc, res = ref.grid_layout(cfg)
+    o2, s2, r2 = enc.level_table()
+    assert enc.n_params() == n_params and list(off) == o2 and list(res) == r2
+    assert np.array_equal(np.asarray(s2, np.float32), sc)
+    D = case[0]
+    n = 4096
+    x = ref.pcg32_floats(1337, 0, n * D).reshape(n, D)
+    x[:8] = 0.0; x[8:16] = 1.0; x[16:24] = 0.5          # cell-boundary edge cases
+    xd = _cuda(x)
+    for level in range(case[1]):
+        idx, w = enc.corners(xd, level)
+        ridx, rw = ref.grid_corners(cfg, x, level)
+        assert np.array_equal(idx.cpu().numpy().view(np.uint32), ridx), f"level {level}"
+        assert np.array_equal(w.cpu().numpy(), rw), f"level {level}"
+
+
+@pytest.mark.parametrize("case", GRID_CASES)
+@pytest.mark.parametrize("layout", [0, 1])
+def test_grid_forward(ops, ref, case, layout):
+    enc, cfg = _grid(ops, ref, case)
+    D = case[0]
+    n = 8192 + 24     # ragged: not a multiple of the 8-row group
+    rng = np.random.default_rng(7)
+    table = rng.uniform(-1, 1, enc.n_params()).astype(np.float16)
+    x = ref.pcg32_floats(1337, 5, n * D).reshape(n, D)
+    C = enc.padded_output_width()
+    y = enc.forward(_cuda(table), _cuda(x), layout)
+    if layout == 1:
+        npad = (n + 7) // 8 * 8
+        y = ops.blk8_to_rowmajor(y, npad, C)[:n]
+    y = y.float().cpu().numpy()
+    yr = ref.grid_forward(cfg, table, x, C).astype(np.float32)
+    err = np.abs(y - yr) / np.maximum(np.abs(yr), 1e-2)
+    assert err.max() <= ENC_TOL, err.max()
+    assert (y[:, case[1] * case[2]:] == 0).all()
+
+
+def test_grid_forward_empty(ops, ref):
+    enc, cfg = _grid(ops, ref, GRID_CASES[0])
+    table = torch.zeros(enc.n_params(), dtype=torch.float16, device="cuda")
+    y = enc.forward(table, torch.zeros(0, 3, device="cuda"))
+    assert y.shape[0] == 0
+
+
+@pytest.mark.parametrize("case", GRID_CASES)
+def test_grid_backward_scatter(ops, ref, case):
+    enc, cfg = _grid(ops, ref, case)
+    D, L, F = case[0], case[1], case[2]
+    n = 16384
+    rng = np.random.default_rng(11)
+    x = ref.pcg32_floats(1338, 0, n * D).reshape(n, D)
+    C = enc.padded_output_width()
+    dy = np.zeros((n, C), np.float16)
+    dy[:, :L * F] = (rng.normal(0, 1, (n, L * F)) / 128).astype(np.float16)
+    dy[100:200] = 0      # all-zero rows are skipped
+    g = enc.backward(_cuda(x), _cuda(dy)).float().cpu().numpy().astype(np.float64)
+    gr = ref.grid_backward(cfg, x, dy, enc.n_params())
+    gabs = ref.grid_backward(cfg, x, np.abs(dy), enc.n_params())     # sum |contrib| bound
+    tol = 2.0 ** -9 * gabs + 1e-6                                    # fp16 atomics: one rounding per accumulated term
+    bad = np.abs(g - gr) > tol
+    assert bad.mean() < 1e-4, (bad.sum(), np.abs(g - gr).max())
+    # conservation: sum of all gradients of a level == sum of dy of that level (weights sum to 1)
+    _, off, _, _ = ref.grid_layout(cfg)
+    for l in range(L):
+        gl = g[off[l] * F:off[l + 1] * F].reshape(-1, F).sum(0)
+        np.testing.assert_allclose(gl, dy[:, l * F:(l + 1) * F].astype(np.float64).sum(0), atol=0.05)
+
+
+def test_grid_backward_input(ops, ref):
+    case = (3, 8, 2, 14, 16, 1.5)
+    enc, cfg = _grid(ops, ref, case)
+    n = 2048
+    rng = np.random.default_rng(12)
+    table = rng.uniform(-1, 1, enc.n_params()).astype(np.float16)
+    x = rng.uniform(0, 1, (n, 3)).astype(np.float32)
+    dy = rng.normal(0, 1, (n, 16)).astype(np.float16)
+    dx = enc.backward_input(_cuda(table), _cuda(x), _cuda(dy)).cpu().numpy()
+    dxr = ref.grid_backward_input(cfg, table, x, dy)
+    np.testing.assert_allclose(dx, dxr, rtol=2e-3, atol=2e-2)
+
+
+def _nerf(ops, ref, cfg_json, seed=1337, scale_grid=1.0):
+    net = ops.NerfNetwork(cfg_json)
+    rcfg = ref.nerf_cfg_from_json(cfg_json)
+    n_params, od, orr, og = ref.nerf_n_params(rcfg)
+    assert net.n_params() == n_params and (net.off_density, net.off_rgb, net.off_encoding) == (od, orr, og)
+    return net, rcfg
+
+
+@pytest.mark.parametrize("cfg_json", [NERF_CFG_16x2, NERF_CFG_FORK])
+def test_nerf_network_init_matches_oracle(ops, ref, cfg_json):
+    net, rcfg = _nerf(ops, ref, cfg_json)
+    p = net.initialize_params(1337).cpu().numpy()
+    pr = ref.nerf_init(rcfg, 1337)
+    assert np.array_equal(p, pr)
+    assert np.abs(p[net.off_encoding:]).max() <= 1e-4
+
+
+def _random_params(net, rng):
+    # trained-like magnitudes: MLP weights ~ xavier, table ~ U(-1,1)/4 so every layer is exercised
+    p = np.empty(net.n_params(), np.float32)
+    p[:net.n_matrix_params] = rng.uniform(-0.25, 0.25, net.n_matrix_params)
+    p[net.n_matrix_params:] = rng.uniform(-0.5, 0.5, net.n_params() - net.n_matrix_params)
+    return p.astype(np.float16)
+
+
+def _coords(ref, n, seed=3):
+    c = ref.pcg32_floats(seed, 0, n * 7).reshape(n, 7).copy()
+    return c
+
+
+@pytest.mark.parametrize("cfg_json", [NERF_CFG_16x2, NERF_CFG_FORK])
+def test_nerf_network_inference(ops, ref, cfg_json):
+    net, rcfg = _nerf(ops, ref, cfg_json)
+    rng = np.random.default_rng(21)
+    params = _random_params(net, rng)
+    n = 1024
+    coords = _coords(ref, n)
+    out = net.inference(_cuda(params), _cuda(coords)).float().cpu().numpy()
+    outr = ref.nerf_forward(rcfg, params, coords).astype(np.float32)
+    err = np.abs(out - outr) / np.maximum(np.abs(outr), 1.0)
+    assert err.max() <= MLP_TOL, (err.max(), out[:2], outr[:2])
+    dens = net.density(_cuda(params), _cuda(coords[:, :3].copy())).float().cpu().numpy()
+    np.testing.assert_allclose(dens, outr[:, 3], rtol=MLP_TOL, atol=MLP_TOL)
+
+
+@pytest.mark.parametrize("cfg_json", [NERF_CFG_16x2, NERF_CFG_FORK])
+def test_nerf_network_forward_backward(ops, ref, cfg_json):
+    net, rcfg = _nerf(ops, ref, cfg_json)
+    rng = np.random.default_rng(22)
+    params = _random_params(net, rng)
+    n = 512
+    coords = _coords(ref, n, seed=4)
+    dL = (rng.normal(0, 1, (n, 4)) / 64).astype(np.float16)
+    dL[n - 128:] = 0      # a padded tail tile contributes nothing
+    g = net.forward_backward(_cuda(params), _cuda(coords), _cuda(dL)).float().cpu().numpy().astype(np.float64)
+    gr = ref.nerf_backward(rcfg, params, coords, dL)
+    nm = net.n_matrix_params
+    # MLP weight gradients: fp32 tensor-core accumulation, one fp16 rounding at the end
+    scale = np.abs(gr[:nm]).max()
+    assert np.abs(g[:nm] - gr[:nm]).max() <= 1e-2 * scale, (np.abs(g[:nm] - gr[:nm]).max(), scale)
+    # per-layer relative L2 error
+    num = np.linalg.norm(g[:nm] - gr[:nm]); den = np.linalg.norm(gr[:nm])
+    assert num <= 5e-3 * den, (num, den)
+    # hash-table gradients
+    gh, ghr = g[nm:], gr[nm:]
+    assert np.linalg.norm(gh - ghr) <= 1e-2 * np.linalg.norm(ghr), (np.linalg.norm(gh - ghr), np.linalg.norm(ghr))
+    assert ((gh != 0) == (np.abs(ghr) > 0)).mean() > 0.999
+
+
+def test_encoded_mlp_image_network(ops, ref):
+    cfg_json = {"encoding": {"otype": "HashGrid", "n_levels": 16, "n_features_per_level": 2, "log2_hashmap_size": 15, "base_resolution": 16},
+                "network": {"otype": "FullyFusedMLP", "activation": "ReLU", "output_activation": "None", "n_neurons": 64, "n_hidden_layers": 2}}
+    net = ops.NetworkWithInputEncoding(cfg_json, 2, 3)
+    gcfg = ref.grid_cfg_from_json(cfg_json["encoding"], 2)
+    rng = np.random.default_rng(31)
+    nm = net.n_matrix_params
+    params = np.concatenate([rng.uniform(-0.25, 0.25, nm), rng.uniform(-0.5, 0.5, net.n_params() - nm)]).astype(np.float16)
+    n = 768
+    x = rng.uniform(0, 1, (n, 2)).astype(np.float32)
+    out = net.inference(_cuda(params), _cuda(x)).float().cpu().numpy()
+    enc = ref.grid_forward(gcfg, params[nm:], x, 32)
+    outr, acts = ref.mlp_forward(params[:nm], 32, 2, enc, want_acts=True)
+    err = np.abs(out - outr.astype(np.float32)) / np.maximum(np.abs(outr.astype(np.float32)), 1.0)
+    assert err.max() <= MLP_TOL, err.max()
+    dL = np.zeros((n, 16), np.float16); dL[:, :3] = rng.normal(0, 1, (n, 3)) / 64
+    g = net.forward_backward(_cuda(params), _cuda(x), _cuda(dL)).float().cpu().numpy().astype(np.float64)
+    din, wg = ref.mlp_backward(params[:nm], 32, 2, enc, acts, dL)
+    assert np.linalg.norm(g[:nm] - wg) <= 5e-3 * np.linalg.norm(wg)
+    gh = ref.grid_backward(gcfg, x, din, net.n_params() - nm)
+    assert np.linalg.norm(g[nm:] - gh) <= 1e-2 * np.linalg.norm(gh)
+
+
+def test_adam_step_matches_oracle(ops, ref):
+    rng = np.random.default_rng(41)
+    n, nm = 50000, 7168
+    master = rng.normal(0, 0.1, n).astype(np.float32)
+    params = master.astype(np.float16)
+    m = np.zeros(n, np.float32); v = np.zeros(n, np.float32); steps = np.zeros(n, np.uint32)
+    ema = np.zeros(n, np.float32); ema_h = np.zeros(n, np.float16)
+    d = [_cuda(a) for a in (master, params, m, v)]
+    dsteps = _cuda(steps.view(np.int32)); dema = _cuda(ema); dema_h = _cuda(ema_h)
+    cfg = ref.AdamCfg(1e-2, 0.9, 0.99, 1e-15, 1e-6, 128.0, nm, 1, 1)
+    for step in range(1, 4):
+        grads = (rng.normal(0, 1, n) * (rng.uniform(size=n) < 0.3)).astype(np.float16)
+        ops.adam_step(d[0], d[1], _cuda(grads), d[2], d[3], dsteps, learning_rate=1e-2, beta1=0.9, beta2=0.99, epsilon=1e-15, l2_reg=1e-6,
+                      loss_scale=128.0, n_matrix_params=nm, ema=dema, ema_half=dema_h, ema_decay=0.95, ema_step=step)
+        ref.adam_step(cfg, master, params, grads, m, v, steps)
+        ref.lib().ref_ema_step(n, 0.95, step, ref.P(params), ref.P(ema), ref.P(ema_h))
+    assert np.array_equal(dsteps.cpu().numpy().view(np.uint32), steps)
+    np.testing.assert_allclose(d[0].cpu().numpy(), master, rtol=1e-5, atol=1e-7)
+    np.testing.assert_allclose(d[2].cpu().numpy(), m, rtol=1e-5, atol=1e-9)
+    np.testing.assert_allclose(dema.cpu().numpy(), ema, rtol=1e-4, atol=1e-6)
+    assert (d[1].cpu().numpy() != params).mean() < 1e-3      # fp16 copies may differ by 1 ulp on rounding ties only

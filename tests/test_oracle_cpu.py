@@ -1,0 +1,205 @@
+"""CPU suite: pins the oracle against known-answer vectors and checks the host-side logic + ABI surface.
+No CUDA device needed (`pytest -m "not gpu"`)."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+
+from .conftest import ROOT
+
+
+def test_pcg32_known_answer(ref):
+    # pcg32 reference demo (pcg-c-basic): seed(42, 54) -> first outputs
+    r = ref.lib()
+    class R(C.Structure):
+        _fields_ = [("state", C.c_uint64), ("inc", C.c_uint64)]
+    rng = R()
+    r.ref_pcg32_seed(C.byref(rng), C.c_uint64(42), C.c_uint64(54))
+    r.ref_pcg32_next_uint.restype = C.c_uint32
+    got = [r.ref_pcg32_next_uint(C.byref(rng)) for _ in range(6)]
+    assert got == [0xa15c02b7, 0x7b47f409, 0xba1d3330, 0x83d2f293, 0xbfa4784b, 0xcbed606e]
+
+
+def test_pcg32_advance_matches_stepping(ref):
+    a = ref.pcg32_floats(1337, 0, 100)
+    b = ref.pcg32_floats(1337, 37, 63)
+    assert np.array_equal(a[37:], b)
+    assert (a >= 0).all() and (a < 1).all()
+
+
+def test_morton_roundtrip(ref):
+    l = ref.lib()
+    l.ref_morton3D.restype = C.c_uint32; l.ref_morton3D_invert.restype = C.c_uint32
+    rng = np.random.default_rng(0)
+    for x, y, z in rng.integers(0, 128, (200, 3)):
+        m = l.ref_morton3D(int(x), int(y), int(z))
+        assert m < 128 ** 3
+        assert (l.ref_morton3D_invert(m), l.ref_morton3D_invert(m >> 1), l.ref_morton3D_invert(m >> 2)) == (x, y, z)
+    assert l.ref_morton3D(1, 0, 0) == 1 and l.ref_morton3D(0, 1, 0) == 2 and l.ref_morton3D(0, 0, 1) == 4
+
+
+def test_grid_layout_matches_survey_sizes(ref):
+    # 16x2, T=2^19, b=1.3819 -> 6 098 120 entries (levels 0-4 dense); fork 4x4 b=2 -> 3.29 M params
+    n, off, sc, res = ref.grid_layout(ref.grid_cfg(3, 16, 2, 19, 16, 1.3819))
+    assert off[-1] == 6098120 and n == 2 * 6098120
+    assert list(res[:3]) == [16, 23, 31] and sc[0] == 15.0
+    n, off, sc, res = ref.grid_layout(ref.grid_cfg(3, 4, 4, 19, 16, 2.0))
+    assert list(res) == [16, 32, 64, 128] and list(np.diff(off)) == [4096, 32768, 262144, 524288]
+    assert n == 4 * (4096 + 32768 + 262144 + 524288)
+
+
+def test_grid_corners_properties(ref):
+    cfg = ref.grid_cfg(3, 16, 2, 19, 16, 2.0)
+    x = ref.pcg32_floats(1337, 0, 3 * 512).reshape(-1, 3)
+    _, off, sc, res = ref.grid_layout(cfg)
+    for level in (0, 3, 5, 15):
+        idx, w = ref.grid_corners(cfg, x, level)
+        size = off[level + 1] - off[level]
+        assert (idx < size).all()
+        np.testing.assert_allclose(w.sum(1), 1.0, rtol=1e-5)
+    # dense level 0: index = x + y*16 + z*256 of the floor cell
+    idx, w = ref.grid_corners(cfg, x, 0)
+    cell = np.floor(x * 15.0 + 0.5).astype(np.int64)
+    assert np.array_equal(idx[:, 0], cell[:, 0] + cell[:, 1] * 16 + cell[:, 2] * 256)
+    # hashed level: prime xor
+    idx, w = ref.grid_corners(cfg, x, 8)
+    s = np.float32(sc[8])
+    cell = np.floor(x * s + np.float32(0.5)).astype(np.uint32)
+    h = (cell[:, 0] ^ (cell[:, 1] * np.uint32(2654435761)) ^ (cell[:, 2] * np.uint32(805459861))) % np.uint32(1 << 19)
+    assert np.array_equal(idx[:, 0], h)
+
+
+def test_grid_forward_backward_adjoint(ref):
+    # <forward(table), dy> == <table, backward(dy)>  (linearity of the encoding in the table)
+    cfg = ref.grid_cfg(3, 8, 2, 14, 16, 1.5)
+    n_params, *_ = ref.grid_layout(cfg)
+    rng = np.random.default_rng(1)
+    table = rng.uniform(-1, 1, n_params).astype(np.float16)
+    x = rng.uniform(0, 1, (300, 3)).astype(np.float32)
+    dy = rng.normal(0, 1, (300, 16)).astype(np.float16)
+    y = ref.grid_forward(cfg, table, x, 16).astype(np.float64)
+    g = ref.grid_backward(cfg, x, dy, n_params)
+    lhs = (y * dy.astype(np.float64)).sum(); rhs = (table.astype(np.float64) * g).sum()
+    assert abs(lhs - rhs) < 2e-2 * max(1.0, abs(rhs))   # y is rounded to fp16
+
+
+def test_grid_input_gradient_finite_difference(ref):
+    cfg = ref.grid_cfg(3, 4, 2, 12, 8, 2.0)
+    n_params, *_ = ref.grid_layout(cfg)
+    rng = np.random.default_rng(2)
+    table = rng.uniform(-1, 1, n_params).astype(np.float16)
+    x = rng.uniform(0.2, 0.8, (50, 3)).astype(np.float32)
+    dy = np.zeros((50, 16), np.float16); dy[:, :8] = rng.normal(0, 1, (50, 8))
+    dx = ref.grid_backward_input(cfg, table, x, dy)
+    eps = 1e-3
+    for d in range(3):
+        xp = x.copy(); xp[:, d] += eps; xm = x.copy(); xm[:, d] -= eps
+        num = ((ref.grid_forward(cfg, table, xp, 16).astype(np.float64) - ref.grid_forward(cfg, table, xm, 16)) * dy).sum(1) / (2 * eps)
+        ok = np.abs(num - dx[:, d]) < 0.05 * np.abs(num).max() + 0.5
+        assert ok.mean() > 0.8   # cells crossed by the +-eps probe break the finite difference for a few points
+
+
+def _np_mlp(w, in_w, nh, x):
+    ws, o, cw = [], 0, in_w
+    for l in range(nh + 1):
+        rows = 16 if l == nh else 64
+        ws.append(w[o:o + rows * cw].reshape(rows, cw).astype(np.float32)); o += rows * cw; cw = 64
+    acts, h = [], x.astype(np.float32)
+    for l in range(nh):
+        h = np.maximum(h @ ws[l].T, 0).astype(np.float16).astype(np.float32); acts.append(h)
+    return (h @ ws[nh].T).astype(np.float16), acts, ws
+
+
+def test_mlp_forward_backward_vs_numpy(ref):
+    rng = np.random.default_rng(3)
+    in_w, nh, n = 32, 2, 64
+    w = rng.normal(0, 0.2, 64 * in_w + 64 * 64 + 16 * 64).astype(np.float16)
+    x = rng.normal(0, 1, (n, in_w)).astype(np.float16)
+    out, acts = ref.mlp_forward(w, in_w, nh, x, want_acts=True)
+    out_np, acts_np, ws = _np_mlp(w, in_w, nh, x)
+    np.testing.assert_allclose(out.astype(np.float32), out_np.astype(np.float32), rtol=2e-3, atol=2e-3)
+    dout = np.zeros((n, 16), np.float16); dout[:, :3] = rng.normal(0, 1, (n, 3))
+    din, wg = ref.mlp_backward(w, in_w, nh, x, acts, dout)
+    # numpy backward in fp32
+    g = dout.astype(np.float32)
+    a = [x.astype(np.float32)] + [acts[l].astype(np.float32) for l in range(nh)]
+    wg_np = []
+    for l in range(nh, -1, -1):
+        wg_np.insert(0, g.T @ a[l])
+        g = g @ ws[l]
+        if l > 0:
+            g = g * (a[l] > 0)
+        g = g.astype(np.float16).astype(np.float32)
+    np.testing.assert_allclose(din.astype(np.float32), g, rtol=1e-2, atol=1e-2)
+    np.testing.assert_allclose(wg, np.concatenate([m.reshape(-1) for m in wg_np]), rtol=1e-3, atol=1e-2)
+
+
+def test_sh4_orthonormality(ref):
+    # Monte-Carlo: int Y_i Y_j dOmega = delta_ij for the 16 real SH basis functions
+    rng = np.random.default_rng(4)
+    v = rng.normal(size=(200000, 3)); v /= np.linalg.norm(v, axis=1, keepdims=True)
+    d = ((v + 1) / 2).astype(np.float32)
+    out = np.zeros((len(d), 16), np.float16)
+    ref.lib().ref_sh4(ref.P(d), C.c_uint32(3), C.c_uint32(len(d)), ref.P(out), C.c_uint32(16))
+    Y = out.astype(np.float64)
+    G = 4 * np.pi * (Y.T @ Y) / len(d)
+    np.testing.assert_allclose(G, np.eye(16), atol=0.03)
+
+
+def test_adam_skips_zero_gradient_hash_entries(ref):
+    n, nm = 64, 16
+    cfg = ref.AdamCfg(1e-2, 0.9, 0.99, 1e-15, 1e-6, 128.0, nm, 1, 1)
+    master = np.linspace(-1, 1, n).astype(np.float32); params = master.astype(np.float16)
+    grads = np.zeros(n, np.float16); grads[::3] = 1.0
+    m = np.zeros(n, np.float32); v = np.zeros(n, np.float32); steps = np.zeros(n, np.uint32)
+    before = master.copy()
+    ref.adam_step(cfg, master, params, grads, m, v, steps)
+    touched = np.arange(n) % 3 == 0
+    hash_part = np.arange(n) >= nm
+    assert (steps[hash_part & ~touched] == 0).all() and (master[hash_part & ~touched] == before[hash_part & ~touched]).all()
+    assert (steps[touched] == 1).all() and (steps[~hash_part] == 1).all()     # matrix params always step (L2 reg)
+    # first Adam step moves by ~lr against the gradient sign
+    np.testing.assert_allclose(before[hash_part & touched] - master[hash_part & touched], 1e-2, rtol=1e-3)
+
+
+def test_exp_decay_schedule(ref):
+    f = ref.lib().ref_exp_decay_lr
+    assert f(1e-2, 19999, 20000, 10000, 0.33, 0xFFFFFFFF) == np.float32(1e-2)
+    np.testing.assert_allclose(f(1e-2, 20000, 20000, 10000, 0.33, 0xFFFFFFFF), 1e-2 * 0.33, rtol=1e-6)
+    np.testing.assert_allclose(f(1e-2, 35000, 20000, 10000, 0.33, 0xFFFFFFFF), 1e-2 * 0.33 ** 2, rtol=1e-6)
+
+
+def test_abi_exports_every_declared_symbol():
+    """include/*.h declares the drop-in boundary; the built library must export each symbol and the ctypes table must
+    cover it (no compute call is made here)."""
+    inc = os.path.join(ROOT, "include")
+    declared = set()
+    for fn in os.listdir(inc):
+        txt = open(os.path.join(inc, fn)).read()
+        txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
+        declared |= set(re.findall(r"\b(ngp_[a-z0-9_]+)\s*\(", txt))
+    assert len(declared) >= 25
+    path = os.path.join(ROOT, "instant-ngp_b200", "libngp_b200.so")
+    assert os.path.exists(path), "run __graft_entry__.build() first"
+    lib = C.CDLL(path)
+    for name in sorted(declared):
+        assert hasattr(lib, name), f"{name} declared in include/ but not exported"
+    import importlib
+    _lib = importlib.import_module("instant-ngp_b200._lib")
+    missing = declared - set(_lib.SYMBOLS) 
+    assert not missing, f"ctypes table lacks {missing}"
+    lib.ngp_abi_version.restype = C.c_int
+    assert lib.ngp_abi_version() == 1
+
+
+def test_product_fails_loudly_without_gpu(ops):
+    import torch
+    if torch.cuda.is_available():
+        return
+    e = ops.Encoding({"otype": "HashGrid", "n_levels": 2}, 3)   # config parsing is host-only and works
+    assert e.n_params() > 0
+    import importlib
+    _lib = importlib.import_module("instant-ngp_b200._lib")
+    st = _lib.lib().ngp_encoding_initialize_params(e._h, None, 1, C.c_void_p(16))
+    assert st != 0 and b"no CUDA device" in _lib.lib().ngp_last_error()
