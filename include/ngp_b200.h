@@ -109,6 +109,66 @@ typedef struct ngp_adam_hyper {
 int ngp_adam_step(void* stream, const ngp_adam_hyper* h, uint64_t n, void* dev_master_fp32, void* dev_params_fp16, const void* dev_grads_fp16,
                   void* dev_m_fp32, void* dev_v_fp32, void* dev_steps_u32, void* dev_ema_fp32 /* nullable */, void* dev_ema_fp16 /* nullable */);
 
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Testbed — replaces the training / inference slice of ngp::Testbed as exposed by the pyngp module
+ * (src/python_api.cu:266-538; include/neural-graphics-primitives/testbed.h:64-516).
+ * ------------------------------------------------------------------------------------------------------------ */
+typedef struct ngp_testbed* ngp_testbed_t;
+enum { NGP_MODE_NERF = 0, NGP_MODE_SDF = 1, NGP_MODE_IMAGE = 2 };             /* ETestbedMode (python_api.cu:271-277) */
+enum { NGP_IMAGE_RGBA8 = 0, NGP_IMAGE_RGBA32F = 1 };                         /* EImageDataType Byte / Float */
+enum { NGP_LENS_PERSPECTIVE = 0, NGP_LENS_OPENCV = 1 };                      /* ELensMode (common.h:243-250) */
+enum { NGP_ACT_NONE = 0, NGP_ACT_RELU = 1, NGP_ACT_LOGISTIC = 2, NGP_ACT_EXPONENTIAL = 3 };   /* ENerfActivation */
+enum { NGP_LOSS_L2 = 0, NGP_LOSS_L1 = 1, NGP_LOSS_MAPE = 2, NGP_LOSS_SMAPE = 3, NGP_LOSS_HUBER = 4, NGP_LOSS_LOGL1 = 5, NGP_LOSS_RELATIVE_L2 = 6 };
+
+/* one training view in HOST memory: what NerfDataset::set_training_image + metadata/xforms hold
+ * (nerf_loader.h:31-46,110-171; python_api.cu:49-67 set_image, :583-605 set_camera_intrinsics/extrinsics).
+ * xform = the NGP-convention camera-to-world mat4x3, column major (x axis, y axis, z axis, position). */
+typedef struct ngp_training_image {
+    const void* pixels; int32_t data_type; int32_t res[2]; float focal_length[2]; float principal_point[2];
+    int32_t lens_mode; float lens_params[4]; float xform[12];
+} ngp_training_image;
+
+typedef struct ngp_train_stats {   /* Testbed.training_step / .loss / nerf.training.counters_rgb */
+    uint32_t training_step; float loss; uint32_t rays_per_batch, measured_batch_size, measured_batch_size_before_compaction, n_rays_total;
+    float learning_rate; float density_grid_mean;
+} ngp_train_stats;
+
+int ngp_testbed_create(int mode, ngp_testbed_t* out);                                   /* Testbed(mode) python_api.cu:388 */
+void ngp_testbed_destroy(ngp_testbed_t t);
+int ngp_testbed_reload_network_from_json(ngp_testbed_t t, const char* json);            /* python_api.cu:402-407 */
+/* load_training_data (python_api.cu:398) with in-memory views; uploads pixels host->device */
+int ngp_testbed_set_nerf_dataset(ngp_testbed_t t, void* stream, uint32_t n_images, const ngp_training_image* images, int32_t aabb_scale);
+int ngp_testbed_set_image(ngp_testbed_t t, void* stream, const float* host_rgba, int32_t width, int32_t height);   /* image mode */
+int ngp_testbed_train(ngp_testbed_t t, void* stream, uint32_t batch_size);              /* Testbed::train, python_api.cu:426 */
+/* data-parallel split of train(): gradients only / optimizer + counters.  Between the two calls the caller all-reduces
+ * (sum) the fp16 gradient buffer; measured_* = 0 keeps the local sample counts for the rays-per-batch control law. */
+int ngp_testbed_train_begin(ngp_testbed_t t, void* stream, uint32_t batch_size);
+int ngp_testbed_train_end(ngp_testbed_t t, void* stream, uint32_t measured_batch_size, uint32_t measured_batch_size_before_compaction);
+int ngp_testbed_set_shard(ngp_testbed_t t, uint32_t rank, uint32_t world_size);
+int ngp_testbed_stats(ngp_testbed_t t, ngp_train_stats* out);
+uint64_t ngp_testbed_n_params(ngp_testbed_t t);                                         /* Testbed::n_params python_api.cu:440 */
+/* device pointers of the trainer's flat buffers (layout nerf_network.h:430-443): 0 master fp32, 1 params fp16,
+ * 2 inference params fp16 (EMA), 3 gradients fp16 */
+int ngp_testbed_param_buffer(ngp_testbed_t t, int which, void** dev_ptr, uint64_t* n_elements);
+/* occupancy grid: 0 density grid fp32 [128^3*(max_cascade+1)], 1 bitfield u8 [128^3*8/8] */
+int ngp_testbed_density_grid(ngp_testbed_t t, int which, void** dev_ptr, uint64_t* n_bytes);
+/* Testbed::render (python_api.cu:127-205) headless: linear premultiplied RGBA float32 rows [y0,y1) of a w x h image,
+ * averaged over spp; camera = mat4x3 column major; out is a HOST buffer unless out_is_device */
+int ngp_testbed_render(ngp_testbed_t t, void* stream, const float* camera_matrix, const float* focal_length, const float* screen_center,
+                       int32_t width, int32_t height, int32_t spp, int32_t y0, int32_t y1, float* rgba_out, int32_t out_is_device, float* depth_out);
+int ngp_testbed_compute_image_mse(ngp_testbed_t t, void* stream, int32_t quantize_to_byte, float* mse_out);   /* python_api.cu:444 */
+/* runtime knobs (pyngp def_readwrite members, python_api.cu:452-537,611-695); value semantics per name:
+ * "random_bg_color","linear_colors","snap_to_pixel_centers","shall_train_encoding","shall_train_network" (bool),
+ * "near_distance","density_grid_decay","render_min_transmittance","cone_angle_constant" (float),
+ * "loss_type","rgb_activation","density_activation" (enum), "seed" (integer), "image_snap_to_pixel_centers",
+ * "image_linear_colors","image_stratified" (bool), "background_r/g/b" (float) */
+int ngp_testbed_set_option(ngp_testbed_t t, const char* name, double value);
+/* parity hook: device pointer + capacity of an internal per-step buffer ("coords","numsteps","ray_indices","rays",
+ * "counters","mlp_out","dloss","coords_compacted","loss","grid_pos","grid_idx","grid_out","mean_density",...) */
+int ngp_testbed_debug_buffer(ngp_testbed_t t, const char* name, void** dev_ptr, uint64_t* n_bytes);
+int ngp_testbed_get_option(ngp_testbed_t t, const char* name, double* value);
+
 #ifdef __cplusplus
 }
 #endif

@@ -41,6 +41,16 @@ class AdamHyper(C.Structure):
                 ("ema_decay", f32), ("ema_step", u32)]
 
 
+class TrainingImage(C.Structure):
+    _fields_ = [("pixels", vp), ("data_type", C.c_int32), ("res", C.c_int32 * 2), ("focal_length", f32 * 2), ("principal_point", f32 * 2),
+                ("lens_mode", C.c_int32), ("lens_params", f32 * 4), ("xform", f32 * 12)]
+
+
+class TrainStats(C.Structure):
+    _fields_ = [("training_step", u32), ("loss", f32), ("rays_per_batch", u32), ("measured_batch_size", u32),
+                ("measured_batch_size_before_compaction", u32), ("n_rays_total", u32), ("learning_rate", f32), ("density_grid_mean", f32)]
+
+
 # name -> (restype, argtypes); every symbol include/ngp_b200.h declares
 SYMBOLS = {
     "ngp_last_error": (cp, []),
@@ -72,6 +82,24 @@ SYMBOLS = {
     "ngp_encoded_mlp_inference": (i32, [vp, vp, vp, vp, u32, u32, vp]),
     "ngp_encoded_mlp_forward_backward": (i32, [vp, vp, vp, vp, u32, u32, vp, vp]),
     "ngp_adam_step": (i32, [vp, C.POINTER(AdamHyper), u64, vp, vp, vp, vp, vp, vp, vp, vp]),
+    "ngp_testbed_create": (i32, [i32, C.POINTER(vp)]),
+    "ngp_testbed_destroy": (None, [vp]),
+    "ngp_testbed_reload_network_from_json": (i32, [vp, cp]),
+    "ngp_testbed_set_nerf_dataset": (i32, [vp, vp, u32, vp, C.c_int32]),
+    "ngp_testbed_set_image": (i32, [vp, vp, vp, C.c_int32, C.c_int32]),
+    "ngp_testbed_train": (i32, [vp, vp, u32]),
+    "ngp_testbed_train_begin": (i32, [vp, vp, u32]),
+    "ngp_testbed_train_end": (i32, [vp, vp, u32, u32]),
+    "ngp_testbed_set_shard": (i32, [vp, u32, u32]),
+    "ngp_testbed_stats": (i32, [vp, C.POINTER(TrainStats)]),
+    "ngp_testbed_n_params": (u64, [vp]),
+    "ngp_testbed_param_buffer": (i32, [vp, i32, C.POINTER(vp), C.POINTER(u64)]),
+    "ngp_testbed_density_grid": (i32, [vp, i32, C.POINTER(vp), C.POINTER(u64)]),
+    "ngp_testbed_render": (i32, [vp, vp, vp, vp, vp, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, vp, C.c_int32, vp]),
+    "ngp_testbed_compute_image_mse": (i32, [vp, vp, C.c_int32, C.POINTER(f32)]),
+    "ngp_testbed_set_option": (i32, [vp, cp, C.c_double]),
+    "ngp_testbed_get_option": (i32, [vp, cp, C.POINTER(C.c_double)]),
+    "ngp_testbed_debug_buffer": (i32, [vp, cp, C.POINTER(vp), C.POINTER(u64)]),
 }
 
 

@@ -1,7 +1,7 @@
 // extern "C" boundary (include/ngp_b200.h): operator-level entry points.  Exceptions never cross the ABI — they are
 // caught, stored per thread and reported as a non-zero status + ngp_last_error().
 #include "../../include/ngp_b200.h"
-#include "network.h"
+#include "testbed.h"
 
 namespace ngp { std::atomic<uint64_t> g_launch_count{0}; }
 
@@ -65,12 +65,12 @@ int ngp_encoding_initialize_params(ngp_encoding_t e, void* stream, uint64_t seed
     NGP_API_END
 }
 int ngp_encoding_forward(ngp_encoding_t e, void* stream, const void* params, const void* x, uint32_t x_stride, uint32_t n, void* y, int y_layout) {
-    NGP_API_BEGIN require_device(); NGP_CHECK(e && params && x && y, "null argument");
+    NGP_API_BEGIN require_device(); NGP_CHECK(e && (n == 0 || (params && x && y)), "null argument");
     grid_forward(S(stream), e->g, H(params), F(x), x_stride, n, H(y), y_layout);
     NGP_API_END
 }
 int ngp_encoding_backward(ngp_encoding_t e, void* stream, const void* x, uint32_t x_stride, uint32_t n, const void* dy, int dy_layout, void* grad) {
-    NGP_API_BEGIN require_device(); NGP_CHECK(e && x && dy && grad, "null argument");
+    NGP_API_BEGIN require_device(); NGP_CHECK(e && (n == 0 || (x && dy && grad)), "null argument");
     grid_backward(S(stream), e->g, F(x), x_stride, n, H(dy), dy_layout, H(grad));
     NGP_API_END
 }
@@ -158,6 +158,126 @@ int ngp_adam_step(void* stream, const ngp_adam_hyper* h, uint64_t n, void* maste
     AdamHyper a{h->learning_rate, h->beta1, h->beta2, h->epsilon, h->l2_reg, h->loss_scale, h->n_matrix_params,
                 h->optimize_matrix_params, h->optimize_non_matrix_params, h->ema_decay, h->ema_step};
     adam_step(S(stream), a, n, F(master), H(params), H(grads), F(m), F(v), reinterpret_cast<uint32_t*>(steps), F(ema), H(ema_half));
+    NGP_API_END
+}
+
+}  // extern "C"
+
+// ---- Testbed ----
+struct ngp_testbed { Testbed tb; explicit ngp_testbed(int mode) : tb(mode) {} };
+
+extern "C" {
+
+int ngp_testbed_create(int mode, ngp_testbed_t* out) {
+    NGP_API_BEGIN NGP_CHECK(out, "null argument");
+    *out = new ngp_testbed(mode);
+    NGP_API_END
+}
+void ngp_testbed_destroy(ngp_testbed_t t) { delete t; }
+int ngp_testbed_reload_network_from_json(ngp_testbed_t t, const char* json) {
+    NGP_API_BEGIN require_device(); NGP_CHECK(t && json, "null argument");
+    t->tb.reload_network_from_json(json);
+    NGP_API_END
+}
+int ngp_testbed_set_nerf_dataset(ngp_testbed_t t, void* stream, uint32_t n_images, const ngp_training_image* images, int32_t aabb_scale) {
+    NGP_API_BEGIN require_device(); NGP_CHECK(t && images, "null argument");
+    static_assert(sizeof(ngp_training_image) == sizeof(HostImage), "ABI struct mismatch");
+    t->tb.set_nerf_dataset(S(stream), n_images, reinterpret_cast<const HostImage*>(images), aabb_scale);
+    NGP_API_END
+}
+int ngp_testbed_set_image(ngp_testbed_t t, void* stream, const float* rgba, int32_t w, int32_t h) {
+    NGP_API_BEGIN require_device(); NGP_CHECK(t && rgba, "null argument");
+    t->tb.set_image(S(stream), rgba, w, h);
+    NGP_API_END
+}
+int ngp_testbed_train(ngp_testbed_t t, void* stream, uint32_t batch) {
+    NGP_API_BEGIN require_device(); NGP_CHECK(t, "null argument");
+    t->tb.train(S(stream), batch);
+    NGP_API_END
+}
+int ngp_testbed_train_begin(ngp_testbed_t t, void* stream, uint32_t batch) {
+    NGP_API_BEGIN require_device(); NGP_CHECK(t, "null argument");
+    t->tb.train_begin(S(stream), batch);
+    NGP_API_END
+}
+int ngp_testbed_train_end(ngp_testbed_t t, void* stream, uint32_t measured, uint32_t measured_before) {
+    NGP_API_BEGIN require_device(); NGP_CHECK(t, "null argument");
+    t->tb.train_end(S(stream), measured, measured_before);
+    NGP_API_END
+}
+int ngp_testbed_set_shard(ngp_testbed_t t, uint32_t rank, uint32_t world) {
+    NGP_API_BEGIN NGP_CHECK(t && world >= 1 && rank < world, "bad shard");
+    t->tb.set_shard(rank, world);
+    NGP_API_END
+}
+int ngp_testbed_stats(ngp_testbed_t t, ngp_train_stats* out) {
+    NGP_API_BEGIN NGP_CHECK(t && out, "null argument");
+    static_assert(sizeof(ngp_train_stats) == sizeof(TrainStats), "ABI struct mismatch");
+    TrainStats st = t->tb.stats(); memcpy(out, &st, sizeof(st));
+    NGP_API_END
+}
+uint64_t ngp_testbed_n_params(ngp_testbed_t t) { return t ? t->tb.n_params() : 0; }
+int ngp_testbed_param_buffer(ngp_testbed_t t, int which, void** ptr, uint64_t* n) {
+    NGP_API_BEGIN NGP_CHECK(t && ptr && n, "null argument");
+    Trainer* tr = t->tb.trainer(); NGP_CHECK(tr, "no network loaded");
+    switch (which) { case 0: *ptr = tr->master; break; case 1: *ptr = tr->params; break; case 2: *ptr = tr->inference_params; break;
+        case 3: *ptr = tr->grads; break; default: throw Error("param_buffer: which must be 0..3"); }
+    *n = tr->n_params;
+    NGP_API_END
+}
+int ngp_testbed_density_grid(ngp_testbed_t t, int which, void** ptr, uint64_t* n_bytes) {
+    NGP_API_BEGIN NGP_CHECK(t && ptr && n_bytes, "null argument");
+    if (which == 0) { *ptr = (void*)t->tb.density_grid(); *n_bytes = (uint64_t)NERF_GRID_N_CELLS * (t->tb.max_cascade() + 1) * 4; }
+    else if (which == 1) { *ptr = (void*)t->tb.density_grid_bitfield(); *n_bytes = (uint64_t)NERF_GRID_N_CELLS * NERF_CASCADES / 8; }
+    else throw Error("density_grid: which must be 0 or 1");
+    NGP_API_END
+}
+int ngp_testbed_render(ngp_testbed_t t, void* stream, const float* cam, const float* focal, const float* center, int32_t w, int32_t h, int32_t spp,
+                       int32_t y0, int32_t y1, float* out, int32_t out_is_device, float* depth) {
+    NGP_API_BEGIN require_device(); NGP_CHECK(t && cam && focal && center && out, "null argument");
+    t->tb.render(S(stream), cam, focal, center, w, h, spp, y0, y1, out, out_is_device != 0, depth);
+    NGP_API_END
+}
+int ngp_testbed_compute_image_mse(ngp_testbed_t t, void* stream, int32_t quantize, float* out) {
+    NGP_API_BEGIN require_device(); NGP_CHECK(t && out, "null argument");
+    *out = t->tb.compute_image_mse(S(stream), quantize != 0);
+    NGP_API_END
+}
+
+int ngp_testbed_debug_buffer(ngp_testbed_t t, const char* name, void** ptr, uint64_t* n_bytes) {
+    NGP_API_BEGIN NGP_CHECK(t && name && ptr && n_bytes, "null argument");
+    t->tb.debug_buffer(name, ptr, n_bytes);
+    NGP_API_END
+}
+
+#define NGP_OPTIONS(X)                                                                                                           \
+    X(random_bg_color, bool) X(linear_colors, bool) X(snap_to_pixel_centers, bool) X(shall_train_encoding, bool) X(shall_train_network, bool) \
+    X(near_distance, float) X(density_grid_decay, float) X(render_min_transmittance, float) X(cone_angle_constant, float)         \
+    X(loss_type, int) X(rgb_activation, int) X(density_activation, int) X(seed, uint64_t)                                        \
+    X(image_snap_to_pixel_centers, bool) X(image_linear_colors, bool) X(image_stratified, bool)
+
+int ngp_testbed_set_option(ngp_testbed_t t, const char* name, double value) {
+    NGP_API_BEGIN NGP_CHECK(t && name, "null argument");
+    const std::string n = name;
+#define X(field, type) if (n == #field) { t->tb.field = (type)value; return 0; }
+    NGP_OPTIONS(X)
+#undef X
+    if (n == "background_r") { t->tb.background_color[0] = (float)value; return 0; }
+    if (n == "background_g") { t->tb.background_color[1] = (float)value; return 0; }
+    if (n == "background_b") { t->tb.background_color[2] = (float)value; return 0; }
+    throw Error("unknown option '" + n + "'");
+    NGP_API_END
+}
+int ngp_testbed_get_option(ngp_testbed_t t, const char* name, double* value) {
+    NGP_API_BEGIN NGP_CHECK(t && name && value, "null argument");
+    const std::string n = name;
+#define X(field, type) if (n == #field) { *value = (double)t->tb.field; return 0; }
+    NGP_OPTIONS(X)
+#undef X
+    if (n == "background_r") { *value = t->tb.background_color[0]; return 0; }
+    if (n == "background_g") { *value = t->tb.background_color[1]; return 0; }
+    if (n == "background_b") { *value = t->tb.background_color[2]; return 0; }
+    throw Error("unknown option '" + n + "'");
     NGP_API_END
 }
 

@@ -1,0 +1,115 @@
+// Image-primitive kernels (replaces src/testbed_image.cu:62-76 stratify2_kernel, :166-212 eval_image_kernel_and_snap,
+// :440-463 image_coords_from_idx / image_mse_kernel) and the tcnn L2 loss used by Trainer::training_step
+// (testbed_image.cu:276).  Sample generation, stratification and target lookup are fused into one kernel.
+#include "image_kernels.h"
+
+namespace ngp {
+
+NGP_D float lin2srgb(float l) { return l < 0.0031308f ? 12.92f * l : 1.055f * powf(l, 0.41666f) - 0.055f; }
+
+NGP_D void image_lookup(const float* __restrict__ image, int W, int H, float& px, float& py, bool snap, bool linear_colors, float* v) {
+    auto read_val = [&](int x, int y, float* o) {
+        const float4 p = __ldg(reinterpret_cast<const float4*>(image) + (size_t)y * W + x);
+        o[0] = linear_colors ? p.x : lin2srgb(p.x); o[1] = linear_colors ? p.y : lin2srgb(p.y); o[2] = linear_colors ? p.z : lin2srgb(p.z);
+    };
+    if (snap) {
+        int ix = (int)floorf(px * (float)W), iy = (int)floorf(py * (float)H);
+        px = ((float)ix + 0.5f) / (float)W; py = ((float)iy + 0.5f) / (float)H;
+        ix = clampi(ix, 0, W - 1); iy = clampi(iy, 0, H - 1);
+        read_val(ix, iy, v);
+    } else {
+        const float fx = fminf(fmaxf(px * (float)W - 0.5f, 0.0f), (float)W - (1.0f + 1e-4f));
+        const float fy = fminf(fmaxf(py * (float)H - 0.5f, 0.0f), (float)H - (1.0f + 1e-4f));
+        int ix = (int)fx, iy = (int)fy; const float wx = fx - (float)ix, wy = fy - (float)iy;
+        ix = clampi(ix, 0, W - 2); iy = clampi(iy, 0, H - 2);
+        float a[3], b[3], c[3], d[3]; read_val(ix, iy, a); read_val(ix + 1, iy, b); read_val(ix, iy + 1, c); read_val(ix + 1, iy + 1, d);
+        for (int k = 0; k < 3; ++k) v[k] = (1 - wx) * (1 - wy) * a[k] + wx * (1 - wy) * b[k] + (1 - wx) * wy * c[k] + wx * wy * d[k];
+    }
+}
+
+// positions: element e of the [n][2] array is float #e of the pcg32 stream (generate_random_uniform), then stratify2_kernel
+__global__ void image_batch_kernel(uint32_t n, Pcg32 rng, uint32_t log2_batch, bool stratify, const float* __restrict__ image, int W, int H, bool snap,
+                                   bool linear_colors, float* __restrict__ pos, float* __restrict__ target) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    rng.advance((int64_t)((uint64_t)i * 2));
+    float px = rng.next_float(), py = rng.next_float();
+    if (stratify) {
+        const uint32_t log2s = log2_batch / 2, size = 1u << log2s;
+        const uint32_t ib = i & ((1u << log2_batch) - 1), x = ib & (size - 1), y = ib >> log2s;
+        px = px / (float)size + ((float)x / (float)size); py = py / (float)size + ((float)y / (float)size);
+    }
+    float v[3]; image_lookup(image, W, H, px, py, snap, linear_colors, v);
+    pos[(size_t)i * 2] = px; pos[(size_t)i * 2 + 1] = py;
+    target[(size_t)i * 3] = v[0]; target[(size_t)i * 3 + 1] = v[1]; target[(size_t)i * 3 + 2] = v[2];
+}
+
+__global__ void image_eval_coords_kernel(uint32_t n, uint32_t offset, const float* __restrict__ image, int W, int H, bool linear_colors,
+                                         float* __restrict__ pos, float* __restrict__ target) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t idx = i + offset;
+    const int x = clampi((int)(idx % (uint32_t)W), 0, W - 1), y = clampi((int)(idx / (uint32_t)W), 0, H - 1);
+    float px = ((float)x + 0.5f) / (float)W, py = ((float)y + 0.5f) / (float)H;
+    float v[3]; image_lookup(image, W, H, px, py, true, linear_colors, v);
+    pos[(size_t)i * 2] = px; pos[(size_t)i * 2 + 1] = py;
+    target[(size_t)i * 3] = v[0]; target[(size_t)i * 3 + 1] = v[1]; target[(size_t)i * 3 + 2] = v[2];
+}
+
+// tcnn L2 loss: value = diff^2 / (n*3), gradient = loss_scale * 2 * diff / (n*3); prediction fp16 [n][16]
+__global__ void l2_loss_kernel(uint32_t n, const __half* __restrict__ pred, const float* __restrict__ target, float loss_scale, __half* __restrict__ dL,
+                               float* __restrict__ loss_values) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float n_total = (float)n * 3.0f;
+    __half2 o[8];
+    float l = 0.f, g[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const float diff = __half2float(pred[(size_t)i * 16 + c]) - target[(size_t)i * 3 + c];
+        l += diff * diff / n_total;
+        g[c] = loss_scale * 2.0f * diff / n_total;
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) o[k] = __floats2half2_rn(0.f, 0.f);
+    o[0] = __floats2half2_rn(g[0], g[1]); o[1] = __floats2half2_rn(g[2], 0.f);
+    reinterpret_cast<uint4*>(dL + (size_t)i * 16)[0] = reinterpret_cast<uint4*>(o)[0];
+    reinterpret_cast<uint4*>(dL + (size_t)i * 16)[1] = reinterpret_cast<uint4*>(o)[1];
+    if (loss_values) loss_values[i] = l;
+}
+
+// image_mse_kernel (testbed_image.cu:452-463)
+__global__ void image_se_kernel(uint32_t n, const float* __restrict__ target, const __half* __restrict__ pred, float* __restrict__ se, bool quantize) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float acc = 0.f;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        float p = __half2float(pred[(size_t)i * 16 + c]);
+        if (quantize) p = (float)clampi((int)(p * 255.0f + 0.5f), 0, 255) / 255.0f;
+        const float d = target[(size_t)i * 3 + c] - p;
+        acc += d * d;
+    }
+    se[i] = acc / 3.0f;
+}
+
+void image_generate_batch(cudaStream_t s, uint32_t n, Pcg32 rng, bool stratify, const float* image, int W, int H, bool snap, bool linear_colors, float* pos, float* target) {
+    uint32_t log2n = 0; while ((1u << log2n) < n) ++log2n;
+    const bool can_stratify = stratify && (1u << log2n) == n && (log2n % 2 == 0);
+    image_batch_kernel<<<div_round_up(n, 256), 256, 0, s>>>(n, rng, log2n, can_stratify, image, W, H, snap, linear_colors, pos, target);
+    NGP_POST_LAUNCH();
+}
+void image_eval_coords(cudaStream_t s, uint32_t n, uint32_t offset, const float* image, int W, int H, bool linear_colors, float* pos, float* target) {
+    image_eval_coords_kernel<<<div_round_up(n, 256), 256, 0, s>>>(n, offset, image, W, H, linear_colors, pos, target);
+    NGP_POST_LAUNCH();
+}
+void l2_loss(cudaStream_t s, uint32_t n, const __half* pred, const float* target, float loss_scale, __half* dL, float* loss_values) {
+    l2_loss_kernel<<<div_round_up(n, 256), 256, 0, s>>>(n, pred, target, loss_scale, dL, loss_values);
+    NGP_POST_LAUNCH();
+}
+void image_squared_error(cudaStream_t s, uint32_t n, const float* target, const __half* pred, float* se, bool quantize) {
+    image_se_kernel<<<div_round_up(n, 256), 256, 0, s>>>(n, target, pred, se, quantize);
+    NGP_POST_LAUNCH();
+}
+
+}  // namespace ngp

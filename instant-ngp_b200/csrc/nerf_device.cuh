@@ -1,0 +1,274 @@
+// Device helpers of the NeRF path: constants, exponential stepping, cascaded occupancy lookups, ray generation,
+// colour conversions, low-discrepancy jitter.  Restates the helper layer of the reference
+// (src/testbed_nerf.cu:55-184,285-315,389-457,614-633; include/.../common_device.cuh:75-121,289-581,885-925;
+// random_val.cuh:151-325; bounding_box.cuh:163-223) for sm_100a; arithmetic order is kept identical to the CPU
+// oracle (no implicit FMA contraction, explicit fmaf where fused) so traversal decisions are bit-exact.
+#pragma once
+#include "ngp_common.cuh"
+
+namespace ngp {
+
+constexpr uint32_t NERF_GRIDSIZE = 128;
+constexpr uint32_t NERF_GRID_N_CELLS = 128u * 128u * 128u;
+constexpr uint32_t NERF_STEPS = 1024;
+constexpr uint32_t NERF_CASCADES = 8;
+constexpr uint32_t N_MAX_RANDOM_SAMPLES_PER_RAY = 16;
+constexpr float NERF_MIN_OPTICAL_THICKNESS = 0.01f;
+constexpr float MAX_DEPTH = 16384.0f;
+constexpr float LOSS_SCALE = 128.0f;
+constexpr float SQRT3 = 1.73205080757f;
+NGP_HD float STEPSIZE() { return SQRT3 / (float)NERF_STEPS; }
+NGP_HD float MIN_CONE_STEPSIZE() { return STEPSIZE(); }
+NGP_HD float MAX_CONE_STEPSIZE() { return STEPSIZE() * (float)(1 << (NERF_CASCADES - 1)) * (float)NERF_STEPS / (float)NERF_GRIDSIZE; }
+
+enum ImageDataType : int { IMG_BYTE = 0, IMG_FLOAT = 1 };
+enum LensMode : int { LENS_PERSPECTIVE = 0, LENS_OPENCV = 1 };
+enum NerfActivation : int { ACT_NONE = 0, ACT_RELU = 1, ACT_LOGISTIC = 2, ACT_EXPONENTIAL = 3 };
+enum LossType : int { LOSS_L2 = 0, LOSS_L1 = 1, LOSS_MAPE = 2, LOSS_SMAPE = 3, LOSS_HUBER = 4, LOSS_LOGL1 = 5, LOSS_RELL2 = 6 };
+
+// TrainingImageMetadata (nerf_loader.h:31-46) + TrainingXForm.start, flattened; lives in device memory
+struct ImageMeta {
+    const void* pixels;
+    int data_type, lens_mode;
+    float lens_params[4];
+    int res[2];
+    float principal_point[2];
+    float focal_length[2];
+    float xform[12];
+};
+
+// ---- stepping (testbed_nerf.cu:124-184) ----
+NGP_HD float to_stepping_space(float t, float cone_angle) {
+    if (cone_angle <= 1e-5f) return t / MIN_CONE_STEPSIZE();
+    float log1p_c = logf(1.0f + cone_angle);
+    float a = (logf(MIN_CONE_STEPSIZE()) - logf(log1p_c)) / log1p_c;
+    float b = (logf(MAX_CONE_STEPSIZE()) - logf(log1p_c)) / log1p_c;
+    float at = expf(a * log1p_c), bt = expf(b * log1p_c);
+    if (t <= at) return (t - at) / MIN_CONE_STEPSIZE() + a;
+    else if (t <= bt) return logf(t) / log1p_c;
+    else return (t - bt) / MAX_CONE_STEPSIZE() + b;
+}
+NGP_HD float from_stepping_space(float n, float cone_angle) {
+    if (cone_angle <= 1e-5f) return n * MIN_CONE_STEPSIZE();
+    float log1p_c = logf(1.0f + cone_angle);
+    float a = (logf(MIN_CONE_STEPSIZE()) - logf(log1p_c)) / log1p_c;
+    float b = (logf(MAX_CONE_STEPSIZE()) - logf(log1p_c)) / log1p_c;
+    float at = expf(a * log1p_c), bt = expf(b * log1p_c);
+    if (n <= a) return (n - a) * MIN_CONE_STEPSIZE() + at;
+    else if (n <= b) return expf(n * log1p_c);
+    else return (n - b) * MAX_CONE_STEPSIZE() + bt;
+}
+NGP_HD float advance_n_steps(float t, float cone_angle, float n) { return from_stepping_space(to_stepping_space(t, cone_angle) + n, cone_angle); }
+NGP_HD float calc_dt(float t, float cone_angle) { return advance_n_steps(t, cone_angle, 1.0f) - t; }
+
+// ---- occupancy lookup (testbed_nerf.cu:433-457,614-633) ----
+NGP_HD uint32_t mip_from_pos(V3 p, uint32_t max_cascade) {
+    int e;
+    float m = fmaxf(fmaxf(fabsf(p.x - 0.5f), fabsf(p.y - 0.5f)), fabsf(p.z - 0.5f));
+    frexpf(m, &e);
+    return (uint32_t)clampi(e + 1, 0, (int)max_cascade);
+}
+NGP_HD uint32_t mip_from_dt(float dt, V3 p, uint32_t max_cascade) {
+    uint32_t mip = mip_from_pos(p, max_cascade);
+    dt *= 2 * NERF_GRIDSIZE;
+    if (dt < 1.0f) return mip;
+    int e;
+    frexpf(dt, &e);
+    // tcnn::clamp(val, lower, upper) = val < lower ? lower : (upper < val ? upper : val)   (testbed_nerf.cu:632)
+    int v = (int)mip; const int lo = e, hi = (int)max_cascade;
+    v = v < lo ? lo : (hi < v ? hi : v);
+    return (uint32_t)v;
+}
+NGP_HD uint32_t cascaded_grid_idx_at(V3 p, uint32_t mip) {
+    float s = scalbnf(1.0f, -(int)mip);
+    p = (p - v3(0.5f, 0.5f, 0.5f)) * s + v3(0.5f, 0.5f, 0.5f);
+    int ix = (int)(p.x * (float)NERF_GRIDSIZE), iy = (int)(p.y * (float)NERF_GRIDSIZE), iz = (int)(p.z * (float)NERF_GRIDSIZE);
+    if (ix < 0 || ix >= (int)NERF_GRIDSIZE || iy < 0 || iy >= (int)NERF_GRIDSIZE || iz < 0 || iz >= (int)NERF_GRIDSIZE) return 0xFFFFFFFFu;
+    return morton3D((uint32_t)ix, (uint32_t)iy, (uint32_t)iz);
+}
+NGP_HD bool density_grid_occupied_at(V3 p, const uint8_t* __restrict__ bitfield, uint32_t mip) {
+    uint32_t idx = cascaded_grid_idx_at(p, mip);
+    if (idx == 0xFFFFFFFFu) return false;
+    return bitfield[idx / 8 + (size_t)NERF_GRID_N_CELLS * mip / 8] & (1 << (idx % 8));
+}
+
+// ---- DDA-like skip (testbed_nerf.cu:285-315) ----
+NGP_HD float distance_to_next_voxel(V3 pos, V3 dir, V3 idir, float res) {
+    V3 p = res * (pos - v3(0.5f, 0.5f, 0.5f));
+    float tx = (floorf(p.x + 0.5f + 0.5f * copysignf(1.0f, dir.x)) - p.x) * idir.x;
+    float ty = (floorf(p.y + 0.5f + 0.5f * copysignf(1.0f, dir.y)) - p.y) * idir.y;
+    float tz = (floorf(p.z + 0.5f + 0.5f * copysignf(1.0f, dir.z)) - p.z) * idir.z;
+    float t = fminf(fminf(tx, ty), tz);
+    return fmaxf(t / res, 0.0f);
+}
+NGP_HD float advance_to_next_voxel(float t, float cone, V3 pos, V3 dir, V3 idir, uint32_t mip) {
+    float res = scalbnf((float)NERF_GRIDSIZE, -(int)mip);
+    float t_target = t + distance_to_next_voxel(pos, dir, idir, res);
+    t = to_stepping_space(t, cone);
+    t_target = to_stepping_space(t_target, cone);
+    return from_stepping_space(t + ceilf(fmaxf(t_target - t, 0.5f)), cone);
+}
+
+// ---- bounding box (bounding_box.cuh:163-223) ----
+NGP_HD bool aabb_contains(const Aabb& b, V3 p) {
+    return p.x >= b.min[0] && p.x <= b.max[0] && p.y >= b.min[1] && p.y <= b.max[1] && p.z >= b.min[2] && p.z <= b.max[2];
+}
+NGP_HD void swapf(float& a, float& b) { float t = a; a = b; b = t; }
+NGP_HD void aabb_ray_intersect(const Aabb& b, V3 o, V3 d, float& out_min, float& out_max) {
+    const float FMAX = 3.402823466e+38f;
+    float tmin = (b.min[0] - o.x) / d.x, tmax = (b.max[0] - o.x) / d.x;
+    if (tmin > tmax) swapf(tmin, tmax);
+    float tymin = (b.min[1] - o.y) / d.y, tymax = (b.max[1] - o.y) / d.y;
+    if (tymin > tymax) swapf(tymin, tymax);
+    if (tmin > tymax || tymin > tmax) { out_min = out_max = FMAX; return; }
+    if (tymin > tmin) tmin = tymin;
+    if (tymax < tmax) tmax = tymax;
+    float tzmin = (b.min[2] - o.z) / d.z, tzmax = (b.max[2] - o.z) / d.z;
+    if (tzmin > tzmax) swapf(tzmin, tzmax);
+    if (tmin > tzmax || tzmin > tmax) { out_min = out_max = FMAX; return; }
+    if (tzmin > tmin) tmin = tzmin;
+    if (tzmax < tmax) tmax = tzmax;
+    out_min = tmin; out_max = tmax;
+}
+NGP_HD V3 warp_position(V3 p, const Aabb& b) { return (p - ld3(b.min)) / (ld3(b.max) - ld3(b.min)); }
+NGP_HD V3 unwarp_position(V3 p, const Aabb& b) { return ld3(b.min) + p * (ld3(b.max) - ld3(b.min)); }
+NGP_HD V3 warp_direction(V3 d) { return (d + v3(1.f, 1.f, 1.f)) * 0.5f; }
+NGP_HD float warp_dt(float dt) {
+    float mx = MIN_CONE_STEPSIZE() * (float)(1 << (NERF_CASCADES - 1));
+    return (dt - MIN_CONE_STEPSIZE()) / (mx - MIN_CONE_STEPSIZE());
+}
+NGP_HD float unwarp_dt(float dt) {
+    float mx = MIN_CONE_STEPSIZE() * (float)(1 << (NERF_CASCADES - 1));
+    return dt * (mx - MIN_CONE_STEPSIZE()) + MIN_CONE_STEPSIZE();
+}
+
+// ---- colour (common_device.cuh:75-121) ----
+NGP_HD float srgb_to_linear(float s) { return s <= 0.04045f ? s / 12.92f : powf((s + 0.055f) / 1.055f, 2.4f); }
+NGP_HD float linear_to_srgb(float l) { return l < 0.0031308f ? 12.92f * l : 1.055f * powf(l, 0.41666f) - 0.055f; }
+
+// ---- network output activations (testbed_nerf.cu:317-387) ----
+NGP_HD float logistic(float x) { return 1.0f / (1.0f + expf(-x)); }
+NGP_HD float network_to_density(float v, int act) {
+    switch (act) { case ACT_NONE: return v; case ACT_RELU: return v > 0.f ? v : 0.f; case ACT_LOGISTIC: return logistic(v); default: return expf(v); }
+}
+NGP_HD float network_to_density_derivative(float v, int act) {
+    switch (act) { case ACT_NONE: return 1.f; case ACT_RELU: return v > 0.f ? 1.f : 0.f;
+        case ACT_LOGISTIC: { float d = logistic(v); return d * (1 - d); } default: return expf(clampf(v, -15.f, 15.f)); }
+}
+NGP_HD float network_to_rgb(float v, int act) {
+    switch (act) { case ACT_NONE: return v; case ACT_RELU: return v > 0.f ? v : 0.f; case ACT_LOGISTIC: return logistic(v);
+        default: return expf(clampf(v, -10.f, 10.f)); }
+}
+NGP_HD float network_to_rgb_derivative(float v, int act) {
+    switch (act) { case ACT_NONE: return 1.f; case ACT_RELU: return v > 0.f ? 1.f : 0.f;
+        case ACT_LOGISTIC: { float d = logistic(v); return d * (1 - d); } default: return expf(clampf(v, -10.f, 10.f)); }
+}
+
+// ---- lens + rays (common_device.cuh:289-377,443-510,545-581) ----
+NGP_HD void opencv_delta(const float* p, float u, float v, float* du, float* dv) {
+    float k1 = p[0], k2 = p[1], p1 = p[2], p2 = p[3];
+    float u2 = u * u, uv = u * v, v2 = v * v, r2 = u2 + v2;
+    float radial = k1 * r2 + k2 * r2 * r2;
+    *du = u * radial + 2.f * p1 * uv + p2 * (r2 + 2.f * u2);
+    *dv = v * radial + 2.f * p2 * uv + p1 * (r2 + 2.f * v2);
+}
+NGP_HD void opencv_undistort(const float* params, float* u, float* v) {
+    const float kMaxStepNorm = 1e-10f, kRelStepSize = 1e-6f, EPS = 1.1920929e-07f;
+    float x0[2] = {*u, *v}, x[2] = {*u, *v};
+    for (uint32_t i = 0; i < 100; ++i) {
+        float step0 = fmaxf(EPS, fabsf(kRelStepSize * x[0])), step1 = fmaxf(EPS, fabsf(kRelStepSize * x[1]));
+        float dx[2], dx0b[2], dx0f[2], dx1b[2], dx1f[2];
+        opencv_delta(params, x[0], x[1], &dx[0], &dx[1]);
+        opencv_delta(params, x[0] - step0, x[1], &dx0b[0], &dx0b[1]);
+        opencv_delta(params, x[0] + step0, x[1], &dx0f[0], &dx0f[1]);
+        opencv_delta(params, x[0], x[1] - step1, &dx1b[0], &dx1b[1]);
+        opencv_delta(params, x[0], x[1] + step1, &dx1f[0], &dx1f[1]);
+        float J00 = 1 + (dx0f[0] - dx0b[0]) / (2 * step0), J10 = (dx1f[0] - dx1b[0]) / (2 * step1);
+        float J01 = (dx0f[1] - dx0b[1]) / (2 * step0), J11 = 1 + (dx1f[1] - dx1b[1]) / (2 * step1);
+        float r0 = x[0] + dx[0] - x0[0], r1 = x[1] + dx[1] - x0[1];
+        float inv_det = 1.0f / (J00 * J11 - J10 * J01);
+        float s0 = (J11 * r0 - J10 * r1) * inv_det, s1 = (-J01 * r0 + J00 * r1) * inv_det;
+        x[0] -= s0; x[1] -= s1;
+        if (s0 * s0 + s1 * s1 < kMaxStepNorm) break;
+    }
+    *u = x[0]; *v = x[1];
+}
+// uv -> unnormalised ray; default args of uv_to_ray (no foveation / parallax / aperture / near plane)
+NGP_HD void uv_to_ray(const float* xform, const int* res, const float* focal, const float* principal, int lens_mode, const float* lens_params,
+                      float u, float v, V3& o, V3& d) {
+    V3 dir = {(u - principal[0]) * (float)res[0] / focal[0], (v - principal[1]) * (float)res[1] / focal[1], 1.0f};
+    if (lens_mode == LENS_OPENCV) opencv_undistort(lens_params, &dir.x, &dir.y);
+    d = mat3_mul(xform, dir);
+    o = v3(xform[9], xform[10], xform[11]);
+}
+NGP_HD void pos_to_uv(const ImageMeta& im, V3 pos, float* uv) {
+    const float* m = im.xform;
+    V3 dir = pos - v3(m[9], m[10], m[11]);
+    float a = m[0], b = m[3], c = m[6], d_ = m[1], e = m[4], f = m[7], g = m[2], h = m[5], i = m[8];
+    float det = a * (e * i - f * h) - b * (d_ * i - f * g) + c * (d_ * h - e * g);
+    float id = 1.0f / det;
+    V3 r = {((e * i - f * h) * dir.x + (c * h - b * i) * dir.y + (b * f - c * e) * dir.z) * id,
+            ((f * g - d_ * i) * dir.x + (a * i - c * g) * dir.y + (c * d_ - a * f) * dir.z) * id,
+            ((d_ * h - e * g) * dir.x + (b * g - a * h) * dir.y + (a * e - b * d_) * dir.z) * id};
+    r.x /= r.z; r.y /= r.z;
+    float du = 0.f, dv = 0.f;
+    if (im.lens_mode == LENS_OPENCV) opencv_delta(im.lens_params, r.x, r.y, &du, &dv);
+    r.x += du; r.y += dv;
+    uv[0] = r.x * im.focal_length[0] / (float)im.res[0] + im.principal_point[0];
+    uv[1] = r.y * im.focal_length[1] / (float)im.res[1] + im.principal_point[1];
+}
+// read_rgba (common_device.cuh:885-925): RGBA8 is sRGB, returned linear & premultiplied; 0x00FF00FF marks masked pixels
+NGP_D void read_rgba(const ImageMeta& im, float u, float v, float* rgba) {
+    int px = clampi((int)(u * (float)im.res[0]), 0, im.res[0] - 1);
+    int py = clampi((int)(v * (float)im.res[1]), 0, im.res[1] - 1);
+    size_t idx = (size_t)px + (size_t)py * im.res[0];
+    if (im.data_type == IMG_BYTE) {
+        uint32_t val = __ldg(reinterpret_cast<const uint32_t*>(im.pixels) + idx);
+        if (val == 0x00FF00FFu) { rgba[0] = rgba[1] = rgba[2] = rgba[3] = -1.0f; return; }
+        float alpha = (float)(val >> 24) * (1.0f / 255.0f);
+        rgba[0] = srgb_to_linear((float)(val & 0xFF) * (1.0f / 255.0f)) * alpha;
+        rgba[1] = srgb_to_linear((float)((val >> 8) & 0xFF) * (1.0f / 255.0f)) * alpha;
+        rgba[2] = srgb_to_linear((float)((val >> 16) & 0xFF) * (1.0f / 255.0f)) * alpha;
+        rgba[3] = alpha;
+    } else {
+        float4 p = __ldg(reinterpret_cast<const float4*>(im.pixels) + idx);
+        rgba[0] = p.x; rgba[1] = p.y; rgba[2] = p.z; rgba[3] = p.w;
+    }
+}
+
+// ---- Owen-scrambled Sobol (random_val.cuh:151-291; Burley 2019) ----
+NGP_HD uint32_t sobol_dim(uint32_t index, uint32_t dim) {
+    uint32_t X = 0, v = 0x80000000u;
+    for (uint32_t bit = 0; bit < 32; ++bit) {
+        if ((index >> bit) & 1u) X ^= v;
+        v = (dim == 0) ? (v >> 1) : (v ^ (v >> 1));
+    }
+    return X;
+}
+NGP_HD uint32_t hash_combine(uint32_t seed, uint32_t v) { return seed ^ (v + (seed << 6) + (seed >> 2)); }
+NGP_HD uint32_t reverse_bits32(uint32_t x) {
+    x = (((x & 0xaaaaaaaau) >> 1) | ((x & 0x55555555u) << 1)); x = (((x & 0xccccccccu) >> 2) | ((x & 0x33333333u) << 2));
+    x = (((x & 0xf0f0f0f0u) >> 4) | ((x & 0x0f0f0f0fu) << 4)); x = (((x & 0xff00ff00u) >> 8) | ((x & 0x00ff00ffu) << 8));
+    return (x >> 16) | (x << 16);
+}
+NGP_HD uint32_t laine_karras(uint32_t x, uint32_t seed) {
+    x += seed; x ^= x * 0x6c50b47cu; x ^= x * 0xb82f1e52u; x ^= x * 0xc7afe638u; x ^= x * 0x8d22f6e6u; return x;
+}
+NGP_HD uint32_t nus_base2(uint32_t x, uint32_t seed) { x = reverse_bits32(x); x = laine_karras(x, seed); return reverse_bits32(x); }
+NGP_HD float ld_random_val(uint32_t index, uint32_t seed) {
+    const float S = (float)(1.0 / (double)(1ull << 32));
+    index = nus_base2(index, seed);
+    return (float)nus_base2(sobol_dim(index, 0), hash_combine(seed, 0)) * S;
+}
+NGP_HD void ld_random_val_2d(uint32_t index, uint32_t seed, float* out) {
+    const float S = (float)(1.0 / (double)(1ull << 32));
+    index = nus_base2(index, seed);
+    for (uint32_t i = 0; i < 2; ++i) out[i] = (float)nus_base2(sobol_dim(index, i), hash_combine(seed, i)) * S;
+}
+NGP_HD void ld_random_pixel_offset(uint32_t spp, float* off) {
+    float a[2], b[2];
+    ld_random_val_2d(0, 0xdeadbeefu, a); ld_random_val_2d(spp, 0xdeadbeefu, b);
+    for (int i = 0; i < 2; ++i) { float o = 0.5f - a[i] + b[i]; off[i] = o - floorf(o); }
+}
+
+}  // namespace ngp

@@ -1,0 +1,667 @@
+// NeRF-specific kernels for sm_100a: occupancy grid maintenance, training ray marcher with deterministic
+// (prefix-scan) sample compaction, volume-rendering loss + analytic gradients, wavefront inference tracer.
+// Each kernel cites the reference kernel it replaces (src/testbed_nerf.cu).  The reference compacts with global
+// atomicAdd (nondeterministic sample order); here block-level warp-shuffle scans + a one-block scan of
+// the block totals give the same set of samples in ray order, so results are reproducible and comparable per slot.
+#include "nerf_kernels.h"
+
+namespace ngp {
+
+constexpr uint32_t SCAN_BLOCK = 256;
+
+// exclusive scan of one value per thread over a 256-thread block; returns the prefix, `total` = block sum (all threads)
+NGP_D uint32_t block_exclusive_scan(uint32_t v, uint32_t& total) {
+    __shared__ uint32_t warp_sums[SCAN_BLOCK / 32];
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { uint32_t n = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += n; }
+    if (lane == 31) warp_sums[warp] = inc;
+    __syncthreads();
+    uint32_t ws = (lane < SCAN_BLOCK / 32) ? warp_sums[lane] : 0;
+#pragma unroll
+    for (int o = 1; o < SCAN_BLOCK / 32; o <<= 1) { uint32_t n = __shfl_up_sync(0xffffffffu, ws, o); if (lane >= o) ws += n; }
+    const uint32_t warp_prefix = __shfl_sync(0xffffffffu, ws, warp) - __shfl_sync(0xffffffffu, (lane < SCAN_BLOCK / 32) ? warp_sums[lane] : 0, warp);
+    total = __shfl_sync(0xffffffffu, ws, SCAN_BLOCK / 32 - 1);
+    __syncthreads();
+    return warp_prefix + inc - v;
+}
+
+// one block: in-place exclusive scan of up to 2 arrays of block totals; grand totals written to out0/out1 (optional)
+__global__ void __launch_bounds__(1024) scan_block_totals_kernel(uint32_t n, uint32_t* a, uint32_t* b, uint32_t* out_a, uint32_t* out_b, bool accumulate_b) {
+    __shared__ uint32_t sh[2][32];
+    uint32_t carry_a = 0, carry_b = 0;
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (uint32_t base = 0; base < n; base += 1024) {
+        const uint32_t i = base + threadIdx.x;
+        uint32_t va = (i < n) ? a[i] : 0, vb = (b && i < n) ? b[i] : 0;
+        uint32_t ia = va, ib = vb;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t na = __shfl_up_sync(0xffffffffu, ia, o), nb = __shfl_up_sync(0xffffffffu, ib, o);
+            if (lane >= o) { ia += na; ib += nb; }
+        }
+        if (lane == 31) { sh[0][warp] = ia; sh[1][warp] = ib; }
+        __syncthreads();
+        uint32_t wa = sh[0][lane], wb = sh[1][lane];
+        uint32_t sa = wa, sb = wb;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t na = __shfl_up_sync(0xffffffffu, sa, o), nb = __shfl_up_sync(0xffffffffu, sb, o);
+            if (lane >= o) { sa += na; sb += nb; }
+        }
+        const uint32_t pa = __shfl_sync(0xffffffffu, sa - wa, warp), pb = __shfl_sync(0xffffffffu, sb - wb, warp);
+        const uint32_t ta = __shfl_sync(0xffffffffu, sa, 31), tb = __shfl_sync(0xffffffffu, sb, 31);
+        if (i < n) { a[i] = carry_a + pa + ia - va; if (b) b[i] = carry_b + pb + ib - vb; }
+        carry_a += ta; carry_b += tb;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        if (out_a) *out_a = carry_a;
+        if (out_b) { if (accumulate_b) *out_b += carry_b; else *out_b = carry_b; }
+    }
+}
+
+// =================================================================================================================
+// Occupancy grid
+// =================================================================================================================
+// mark_untrained_density_grid (testbed_nerf.cu:503-592)
+__global__ void mark_untrained_kernel(uint32_t n_elements, float* __restrict__ grid, uint32_t n_images, const ImageMeta* __restrict__ metas, bool clear_visible) {
+    const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x;
+    if (i >= n_elements) return;
+    if (grid[i] == -1.0f) return;
+    const uint32_t level = i / NERF_GRID_N_CELLS, pos_idx = i % NERF_GRID_N_CELLS;
+    const uint32_t x = morton3D_invert(pos_idx >> 0), y = morton3D_invert(pos_idx >> 1), z = morton3D_invert(pos_idx >> 2);
+    const float voxel_size = scalbnf(1.0f / NERF_GRIDSIZE, (int)level);
+    const V3 pos = (v3((float)x, (float)y, (float)z) * (1.0f / (float)NERF_GRIDSIZE) - v3(0.5f, 0.5f, 0.5f)) * scalbnf(1.0f, (int)level) + v3(0.5f, 0.5f, 0.5f);
+    uint32_t count = 0;
+    for (uint32_t j = 0; j < n_images && count < 1; ++j) {
+        const ImageMeta& m = metas[j];
+        const V3 campos = v3(m.xform[9], m.xform[10], m.xform[11]), fwd = v3(m.xform[6], m.xform[7], m.xform[8]);
+        for (uint32_t k = 0; k < 8; ++k) {
+            const V3 corner = pos + v3((k & 1) ? voxel_size : 0.f, (k & 2) ? voxel_size : 0.f, (k & 4) ? voxel_size : 0.f);
+            const V3 dir = normalize3(corner - campos);
+            if (dot3(dir, fwd) < 1e-4f) continue;
+            float uv[2]; pos_to_uv(m, corner, uv);
+            V3 ro, rd; uv_to_ray(m.xform, m.res, m.focal_length, m.principal_point, m.lens_mode, m.lens_params, uv[0], uv[1], ro, rd);
+            const V3 rdn = normalize3(rd);
+            if (uv[0] > 0.0f && uv[1] > 0.0f && uv[0] < 1.0f && uv[1] < 1.0f && length3(rdn - dir) < 1e-3f) { ++count; break; }
+        }
+    }
+    if (clear_visible || (grid[i] < 0) != (count < 1)) grid[i] = (count >= 1) ? 1.f : -1.f;
+    else grid[i] = 1.0f;
+}
+
+// generate_grid_samples_nerf_nonuniform (testbed_nerf.cu:635-676)
+__global__ void grid_samples_kernel(uint32_t n_elements, Pcg32 rng, uint32_t step, Aabb aabb, const float* __restrict__ grid_in,
+                                    float* __restrict__ pos_out, uint32_t* __restrict__ indices, uint32_t n_cascades, float thresh) {
+    const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x;
+    if (i >= n_elements) return;
+    rng.advance((int64_t)((uint64_t)i * 4));
+    const uint32_t level = (uint32_t)(rng.next_float() * n_cascades) % n_cascades;
+    uint32_t idx = 0;
+    for (int j = 0; j < 10; ++j) {
+        idx = ((i + step * n_elements) * 56924617u + (uint32_t)j * 19349663u + 96925573u) % NERF_GRID_N_CELLS;
+        idx += level * NERF_GRID_N_CELLS;
+        if (grid_in[idx] > thresh) break;
+    }
+    const uint32_t pos_idx = idx % NERF_GRID_N_CELLS;
+    const uint32_t x = morton3D_invert(pos_idx >> 0), y = morton3D_invert(pos_idx >> 1), z = morton3D_invert(pos_idx >> 2);
+    const float r0 = rng.next_float(), r1 = rng.next_float(), r2 = rng.next_float();
+    const V3 pos = ((v3((float)x, (float)y, (float)z) + v3(r0, r1, r2)) * (1.0f / (float)NERF_GRIDSIZE) - v3(0.5f, 0.5f, 0.5f)) * scalbnf(1.0f, (int)level) + v3(0.5f, 0.5f, 0.5f);
+    const V3 w = warp_position(pos, aabb);
+    pos_out[(size_t)i * 3] = w.x; pos_out[(size_t)i * 3 + 1] = w.y; pos_out[(size_t)i * 3 + 2] = w.z;
+    indices[i] = idx;
+}
+
+// splat_grid_samples_nerf_max_nearest_neighbor (testbed_nerf.cu:678-702)
+__global__ void splat_kernel(uint32_t n, const uint32_t* __restrict__ indices, const __half* __restrict__ density_raw, float* __restrict__ grid_tmp, int dact) {
+    const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x;
+    if (i >= n) return;
+    const float mlp = network_to_density(__half2float(density_raw[i]), dact);
+    const float optical_thickness = mlp * scalbnf(MIN_CONE_STEPSIZE(), 0);
+    atomicMax(reinterpret_cast<uint32_t*>(&grid_tmp[indices[i]]), __float_as_uint(optical_thickness));
+}
+
+// ema_grid_samples_nerf (testbed_nerf.cu:731-754)
+__global__ void ema_kernel(uint32_t n, float decay, float* __restrict__ grid, const float* __restrict__ tmp) {
+    const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x;
+    if (i >= n) return;
+    const float p = grid[i];
+    grid[i] = (p < 0.f) ? p : fmaxf(p * decay, tmp[i]);
+}
+
+// deterministic sum: 1024 block partials (fixed tree order), then one block adds the partials in fixed order
+template <bool MEAN_CLAMP>
+__global__ void __launch_bounds__(256) partial_sum_kernel(const float* __restrict__ in, uint32_t n, float scale, float* __restrict__ partials) {
+    __shared__ float sh[256];
+    float acc = 0.f;
+    for (uint32_t i = blockIdx.x * 256 + threadIdx.x; i < n; i += gridDim.x * 256) acc += MEAN_CLAMP ? fmaxf(in[i], 0.f) * scale : in[i];
+    sh[threadIdx.x] = acc;
+    __syncthreads();
+    for (uint32_t s = 128; s > 0; s >>= 1) { if (threadIdx.x < s) sh[threadIdx.x] += sh[threadIdx.x + s]; __syncthreads(); }
+    if (threadIdx.x == 0) partials[blockIdx.x] = sh[0];
+}
+__global__ void __launch_bounds__(1024) final_sum_kernel(const float* __restrict__ partials, uint32_t n, float* __restrict__ out) {
+    __shared__ float sh[1024];
+    sh[threadIdx.x] = threadIdx.x < n ? partials[threadIdx.x] : 0.f;
+    __syncthreads();
+    for (uint32_t s = 512; s > 0; s >>= 1) { if (threadIdx.x < s) sh[threadIdx.x] += sh[threadIdx.x + s]; __syncthreads(); }
+    if (threadIdx.x == 0) *out = sh[0];
+}
+
+// grid_to_bitfield (testbed_nerf.cu:762-786)
+__global__ void grid_to_bitfield_kernel(uint32_t n_elements, uint32_t n_nonzero, const float* __restrict__ grid, uint8_t* __restrict__ bitfield,
+                                        const float* __restrict__ mean_density) {
+    const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x;
+    if (i >= n_elements) return;
+    if (i >= n_nonzero) { bitfield[i] = 0; return; }
+    const float thresh = fminf(NERF_MIN_OPTICAL_THICKNESS, *mean_density);
+    const float4 a = reinterpret_cast<const float4*>(grid)[(size_t)i * 2], b = reinterpret_cast<const float4*>(grid)[(size_t)i * 2 + 1];
+    uint8_t bits = 0;
+    bits |= a.x > thresh ? 1 : 0; bits |= a.y > thresh ? 2 : 0; bits |= a.z > thresh ? 4 : 0; bits |= a.w > thresh ? 8 : 0;
+    bits |= b.x > thresh ? 16 : 0; bits |= b.y > thresh ? 32 : 0; bits |= b.z > thresh ? 64 : 0; bits |= b.w > thresh ? 128 : 0;
+    bitfield[i] = bits;
+}
+
+// bitfield_max_pool (testbed_nerf.cu:788-809)
+__global__ void bitfield_max_pool_kernel(uint32_t n_elements, const uint8_t* __restrict__ prev, uint8_t* __restrict__ next) {
+    const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x;
+    if (i >= n_elements) return;
+    const uint2 p = reinterpret_cast<const uint2*>(prev)[i];
+    uint8_t bits = 0;
+#pragma unroll
+    for (uint32_t j = 0; j < 8; ++j) {
+        const uint32_t byte = ((j < 4 ? p.x : p.y) >> (8 * (j & 3))) & 0xFFu;
+        bits |= byte > 0 ? (uint8_t)(1u << j) : 0;
+    }
+    const uint32_t x = morton3D_invert(i >> 0) + NERF_GRIDSIZE / 8, y = morton3D_invert(i >> 1) + NERF_GRIDSIZE / 8, z = morton3D_invert(i >> 2) + NERF_GRIDSIZE / 8;
+    next[morton3D(x, y, z)] |= bits;
+}
+
+void nerf_mark_untrained_grid(cudaStream_t s, uint32_t n, float* grid, uint32_t n_images, const ImageMeta* metas, bool clear_visible) {
+    mark_untrained_kernel<<<div_round_up(n, 128), 128, 0, s>>>(n, grid, n_images, metas, clear_visible);
+    NGP_POST_LAUNCH();
+}
+void nerf_generate_grid_samples(cudaStream_t s, uint32_t n, Pcg32 rng, uint32_t step, Aabb aabb, const float* grid_in, float* pos_out,
+                                uint32_t* indices, uint32_t n_cascades, float thresh) {
+    if (n == 0) return;
+    grid_samples_kernel<<<div_round_up(n, 256), 256, 0, s>>>(n, rng, step, aabb, grid_in, pos_out, indices, n_cascades, thresh);
+    NGP_POST_LAUNCH();
+}
+void nerf_splat_grid_samples(cudaStream_t s, uint32_t n, const uint32_t* indices, const __half* density_raw, float* grid_tmp, int dact) {
+    if (n == 0) return;
+    splat_kernel<<<div_round_up(n, 256), 256, 0, s>>>(n, indices, density_raw, grid_tmp, dact);
+    NGP_POST_LAUNCH();
+}
+void nerf_ema_grid(cudaStream_t s, uint32_t n, float decay, float* grid, const float* tmp) {
+    ema_kernel<<<div_round_up(n, 256), 256, 0, s>>>(n, decay, grid, tmp);
+    NGP_POST_LAUNCH();
+}
+void reduce_sum_f32(cudaStream_t s, const float* in, uint32_t n, float* out_dev, float* partials) {
+    partial_sum_kernel<false><<<1024, 256, 0, s>>>(in, n, 1.0f, partials); NGP_POST_LAUNCH();
+    final_sum_kernel<<<1, 1024, 0, s>>>(partials, 1024, out_dev); NGP_POST_LAUNCH();
+}
+void nerf_update_bitfield(cudaStream_t s, const float* grid, uint32_t n_cascades, uint8_t* bitfield, float* mean_dev, float* partials) {
+    // update_density_grid_mean_and_bitfield (testbed_nerf.cu:3538-3567): mean of max(v,0) over cascade 0
+    partial_sum_kernel<true><<<1024, 256, 0, s>>>(grid, NERF_GRID_N_CELLS, 1.0f / (float)NERF_GRID_N_CELLS, partials); NGP_POST_LAUNCH();
+    final_sum_kernel<<<1, 1024, 0, s>>>(partials, 1024, mean_dev); NGP_POST_LAUNCH();
+    const uint32_t n_bytes = NERF_GRID_N_CELLS / 8 * NERF_CASCADES, n_nonzero = NERF_GRID_N_CELLS / 8 * n_cascades;
+    grid_to_bitfield_kernel<<<div_round_up(n_bytes, 256), 256, 0, s>>>(n_bytes, n_nonzero, grid, bitfield, mean_dev); NGP_POST_LAUNCH();
+    for (uint32_t level = 1; level < NERF_CASCADES; ++level) {
+        bitfield_max_pool_kernel<<<div_round_up(NERF_GRID_N_CELLS / 64, 256), 256, 0, s>>>(NERF_GRID_N_CELLS / 64, bitfield + (size_t)NERF_GRID_N_CELLS * (level - 1) / 8,
+                                                                                          bitfield + (size_t)NERF_GRID_N_CELLS * level / 8);
+        NGP_POST_LAUNCH();
+    }
+}
+
+
+// =================================================================================================================
+// Training sampler: generate_training_samples_nerf (testbed_nerf.cu:1382-1658)
+//   pass 1 (count)  : pick image + pixel, build the ray, clip to the aabb, march the occupancy bitfield counting samples
+//   scan            : exclusive prefix of the per-ray counts (replaces atomicAdd(numsteps_counter, numsteps))
+//   pass 2 (write)  : march again, write NerfCoordinate{warped pos, warped dt, warped dir} at base + j
+// =================================================================================================================
+NGP_D uint32_t image_idx(uint32_t base_idx, uint32_t n_rays, uint32_t n_images) {   // :1317-1338 (no error-map cdf)
+    return ((base_idx * n_images) / n_rays) % n_images;
+}
+NGP_D void random_image_pos_training(Pcg32& rng, const int* res, bool snap, float* uv) {   // :1291-1315
+    uv[0] = rng.next_float(); uv[1] = rng.next_float();
+    if (snap) {
+        uv[0] = ((float)clampi((int)(uv[0] * (float)res[0]), 0, res[0] - 1) + 0.5f) / (float)res[0];
+        uv[1] = ((float)clampi((int)(uv[1] * (float)res[1]), 0, res[1] - 1) + 0.5f) / (float)res[1];
+    }
+}
+
+template <bool WRITE>
+NGP_D uint32_t march_training_ray(V3 o, V3 d, float startt, float cone, const Aabb& aabb, const uint8_t* __restrict__ bitfield, uint32_t max_mip,
+                                  uint32_t limit, float* __restrict__ coords) {
+    const V3 idir = v3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+    const V3 wd = warp_direction(d);
+    uint32_t j = 0; float t = startt; V3 pos;
+    while (aabb_contains(aabb, pos = ray_at(o, d, t)) && j < limit) {
+        const float dt = calc_dt(t, cone);
+        const uint32_t mip = mip_from_dt(dt, pos, max_mip);
+        if (density_grid_occupied_at(pos, bitfield, mip)) {
+            if (WRITE) {
+                float* c = coords + (size_t)j * 7;
+                const V3 wp = warp_position(pos, aabb);
+                c[0] = wp.x; c[1] = wp.y; c[2] = wp.z; c[3] = warp_dt(dt); c[4] = wd.x; c[5] = wd.y; c[6] = wd.z;
+            }
+            ++j; t += dt;
+        } else {
+            t = advance_to_next_voxel(t, cone, pos, d, idir, mip);
+        }
+    }
+    return j;
+}
+
+__global__ void __launch_bounds__(SCAN_BLOCK) sampler_count_kernel(uint32_t n_rays, Aabb aabb, Pcg32 rng, uint32_t n_images, const ImageMeta* __restrict__ metas,
+                                                                   const uint8_t* __restrict__ bitfield, uint32_t max_mip, bool snap, float cone_angle_constant,
+                                                                   uint32_t ray_offset, uint32_t n_rays_global, SamplerBuffers b) {
+    const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x;
+    uint32_t numsteps = 0;
+    if (i < n_rays) {
+        const uint32_t ig = ray_offset + i;
+        const uint32_t img = image_idx(ig, n_rays_global, n_images);
+        const ImageMeta& m = metas[img];
+        rng.advance((int64_t)((uint64_t)ig * N_MAX_RANDOM_SAMPLES_PER_RAY));
+        float uv[2]; random_image_pos_training(rng, m.res, snap, uv);
+        float texel[4]; read_rgba(m, uv[0], uv[1], texel);
+        if (texel[0] >= 0.0f) {   // negative = masked-away pixel (:1430-1435)
+            (void)rng.next_float();   // motionblur_time (:1440)
+            V3 o, du; uv_to_ray(m.xform, m.res, m.focal_length, m.principal_point, m.lens_mode, m.lens_params, uv[0], uv[1], o, du);
+            if (du.x == 0.f && du.y == 0.f && du.z == 0.f) { o = v3(m.xform[9], m.xform[10], m.xform[11]); du = v3(m.xform[6], m.xform[7], m.xform[8]); }
+            const V3 d = normalize3(du);
+            float tmin, tmax; aabb_ray_intersect(aabb, o, d, tmin, tmax);
+            const float cone = cone_angle_constant;   // calc_cone_angle (:114-122)
+            tmin = fmaxf(tmin, 0.0f);
+            const float startt = advance_n_steps(tmin, cone, rng.next_float());
+            numsteps = march_training_ray<false>(o, d, startt, cone, aabb, bitfield, max_mip, NERF_STEPS, nullptr);
+            float* rt = b.ray_tmp + (size_t)i * 8;
+            rt[0] = o.x; rt[1] = o.y; rt[2] = o.z; rt[3] = du.x; rt[4] = du.y; rt[5] = du.z; rt[6] = startt; rt[7] = cone;
+        }
+        b.numsteps_all[i] = numsteps;
+    }
+    uint32_t total_steps, total_rays;
+    block_exclusive_scan(numsteps, total_steps);
+    block_exclusive_scan(numsteps > 0 ? 1u : 0u, total_rays);
+    if (threadIdx.x == 0) { b.block_steps[blockIdx.x] = total_steps; b.block_rays[blockIdx.x] = total_rays; }
+}
+
+__global__ void __launch_bounds__(SCAN_BLOCK) sampler_write_kernel(uint32_t n_rays, Aabb aabb, uint32_t max_samples, const uint8_t* __restrict__ bitfield,
+                                                                   uint32_t max_mip, SamplerBuffers b) {
+    const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x;
+    const uint32_t numsteps = i < n_rays ? b.numsteps_all[i] : 0;
+    uint32_t tot;
+    const uint32_t base = b.block_steps[blockIdx.x] + block_exclusive_scan(numsteps, tot);
+    const uint32_t ray_idx = b.block_rays[blockIdx.x] + block_exclusive_scan(numsteps > 0 ? 1u : 0u, tot);
+    const bool keep = numsteps > 0 && base + numsteps <= max_samples;   // :1616-1619
+    uint32_t kept_total;
+    block_exclusive_scan(keep ? 1u : 0u, kept_total);
+    if (threadIdx.x == 0 && kept_total) atomicAdd(&b.counters[0], kept_total);
+    if (!keep) return;
+    const float* rt = b.ray_tmp + (size_t)i * 8;
+    const V3 o = ld3(rt), du = ld3(rt + 3);
+    b.ray_indices[ray_idx] = i;
+    float* r = b.rays + (size_t)ray_idx * 6;
+    r[0] = o.x; r[1] = o.y; r[2] = o.z; r[3] = du.x; r[4] = du.y; r[5] = du.z;
+    b.numsteps[ray_idx * 2 + 0] = numsteps; b.numsteps[ray_idx * 2 + 1] = base;
+    march_training_ray<true>(o, normalize3(du), rt[6], rt[7], aabb, bitfield, max_mip, numsteps, b.coords + (size_t)base * 7);
+}
+
+void nerf_generate_training_samples(cudaStream_t s, uint32_t n_rays, Aabb aabb, uint32_t max_samples, uint32_t n_rays_total, Pcg32 rng,
+                                    uint32_t n_images, const ImageMeta* metas, const uint8_t* bitfield, uint32_t max_mip, bool snap,
+                                    float cone_angle_constant, uint32_t ray_offset, uint32_t n_rays_global, const SamplerBuffers& b) {
+    (void)n_rays_total;
+    const uint32_t blocks = div_round_up(n_rays, SCAN_BLOCK);
+    sampler_count_kernel<<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, rng, n_images, metas, bitfield, max_mip, snap, cone_angle_constant, ray_offset, n_rays_global, b);
+    NGP_POST_LAUNCH();
+    scan_block_totals_kernel<<<1, 1024, 0, s>>>(blocks, b.block_steps, b.block_rays, &b.counters[1], nullptr, false);
+    NGP_POST_LAUNCH();
+    sampler_write_kernel<<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, max_samples, bitfield, max_mip, b);
+    NGP_POST_LAUNCH();
+}
+
+
+// =================================================================================================================
+// Loss / compositor / gradient: compute_loss_kernel_train_nerf (testbed_nerf.cu:1660-2012) with the default-off features
+// (envmap, error map, depth supervision, exposure, extra dims, max_level_rand_training) left out.
+//   pass 1: front-to-back composite of each ray (T, alpha, rgb), target pixel on the replayed random background
+//   scan  : exclusive prefix of the compacted step counts (replaces atomicAdd(numsteps_counter_compacted, ...))
+//   pass 2: loss + analytic dL/d(rgb,sigma) per kept sample, coordinates copied to the compacted batch
+// =================================================================================================================
+struct LG { V3 loss, grad; };
+NGP_D LG loss_and_gradient(V3 target, V3 pred, int type) {   // :207-283,1340-1355
+    const float d[3] = {pred.x - target.x, pred.y - target.y, pred.z - target.z}, p[3] = {pred.x, pred.y, pred.z}, tg[3] = {target.x, target.y, target.z};
+    float l[3], g[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        switch (type) {
+            case LOSS_RELL2: { float den = p[c] * p[c] + 1e-2f; l[c] = d[c] * d[c] / den; g[c] = 2.0f * d[c] / den; break; }
+            case LOSS_L1: l[c] = fabsf(d[c]); g[c] = copysignf(1.0f, d[c]); break;
+            case LOSS_MAPE: { float den = fabsf(p[c]) + 1e-2f; l[c] = fabsf(d[c]) / den; g[c] = copysignf(1.0f / den, d[c]); break; }
+            case LOSS_SMAPE: { float den = 0.5f * (fabsf(p[c]) + fabsf(tg[c])) + 1e-2f; l[c] = fabsf(d[c]) / den; g[c] = copysignf(1.0f / den, d[c]); break; }
+            case LOSS_HUBER: { const float alpha = 0.1f; float ad = fabsf(d[c]); float sq = 0.5f / alpha * d[c] * d[c];
+                l[c] = (ad > alpha ? (ad - 0.5f * alpha) : sq) / 5.0f;
+                g[c] = (ad > alpha ? (d[c] > 0 ? 1.0f : -1.0f) : (d[c] / alpha)) / 5.0f; break; }
+            case LOSS_LOGL1: { float dv = fabsf(d[c]) + 1.0f; l[c] = logf(dv); g[c] = copysignf(1.0f / dv, d[c]); break; }
+            default: l[c] = d[c] * d[c]; g[c] = 2.0f * d[c]; break;
+        }
+    }
+    return {v3(l[0], l[1], l[2]), v3(g[0], g[1], g[2])};
+}
+
+NGP_D void load_out4(const __half* p, float* o) {
+    const uint2 raw = __ldg(reinterpret_cast<const uint2*>(p));
+    const __half* h = reinterpret_cast<const __half*>(&raw);
+    o[0] = __half2float(h[0]); o[1] = __half2float(h[1]); o[2] = __half2float(h[2]); o[3] = __half2float(h[3]);
+}
+
+__global__ void __launch_bounds__(SCAN_BLOCK) loss_forward_kernel(uint32_t n_rays, Pcg32 rng, LossConfig cfg, uint32_t n_images, const ImageMeta* __restrict__ metas,
+                                                                  uint32_t ray_offset, uint32_t n_rays_global, SamplerBuffers sb, LossBuffers lb) {
+    const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x;
+    uint32_t cn = 0;
+    if (i < sb.counters[0]) {
+        const uint32_t numsteps = sb.numsteps[i * 2 + 0], base = sb.numsteps[i * 2 + 1];
+        const float* cin = sb.coords + (size_t)base * 7;
+        const __half* no = lb.network_output + (size_t)base * 4;
+        float T = 1.f; const float epsilon = 1e-4f;
+        V3 rgb_ray = v3(0, 0, 0);
+        for (; cn < numsteps; ++cn) {
+            if (T < epsilon) break;
+            float o[4]; load_out4(no + (size_t)cn * 4, o);
+            const V3 rgb = v3(network_to_rgb(o[0], cfg.rgb_activation), network_to_rgb(o[1], cfg.rgb_activation), network_to_rgb(o[2], cfg.rgb_activation));
+            const float dt = unwarp_dt(__ldg(cin + (size_t)cn * 7 + 3));
+            const float density = network_to_density(o[3], cfg.density_activation);
+            const float alpha = 1.f - expf(-density * dt);
+            const float weight = alpha * T;
+            rgb_ray = rgb_ray + weight * rgb;
+            T *= (1.f - alpha);
+        }
+        // replay the sampler's RNG stream to recover pixel + background colour (:1757-1780)
+        const uint32_t ig = ray_offset + sb.ray_indices[i];
+        rng.advance((int64_t)((uint64_t)ig * N_MAX_RANDOM_SAMPLES_PER_RAY));
+        const ImageMeta& m = metas[image_idx(ig, n_rays_global, n_images)];
+        float uv[2]; random_image_pos_training(rng, m.res, cfg.snap_to_pixel_centers, uv);
+        rng.advance(1);   // motionblur_time
+        V3 bg = ld3(cfg.background_color);
+        if (cfg.random_bg_color) { const float a = rng.next_float(), b = rng.next_float(), c = rng.next_float(); bg = v3(a, b, c); }
+        bg = v3(srgb_to_linear(bg.x), srgb_to_linear(bg.y), srgb_to_linear(bg.z));
+        float tex[4]; read_rgba(m, uv[0], uv[1], tex);
+        const V3 trgb = v3(tex[0], tex[1], tex[2]); const float ta = tex[3];
+        V3 target;
+        if (cfg.linear_colors) {
+            target = trgb + (1.0f - ta) * bg;
+        } else {
+            bg = v3(linear_to_srgb(bg.x), linear_to_srgb(bg.y), linear_to_srgb(bg.z));
+            if (ta > 0) {
+                const V3 q = v3(linear_to_srgb(trgb.x / ta), linear_to_srgb(trgb.y / ta), linear_to_srgb(trgb.z / ta));
+                target = q * ta + (1.0f - ta) * bg;
+            } else target = bg;
+        }
+        if (cn == numsteps) rgb_ray = rgb_ray + T * bg;
+        float* rs = lb.ray_scratch + (size_t)i * 8;
+        rs[0] = rgb_ray.x; rs[1] = rgb_ray.y; rs[2] = rgb_ray.z; rs[3] = target.x; rs[4] = target.y; rs[5] = target.z;
+        lb.compacted_numsteps[i] = cn;
+    }
+    uint32_t total;
+    block_exclusive_scan(cn, total);
+    if (threadIdx.x == 0) sb.block_steps[blockIdx.x] = total;
+}
+
+__global__ void __launch_bounds__(SCAN_BLOCK) loss_backward_kernel(uint32_t n_rays, Aabb aabb, uint32_t max_compacted, LossConfig cfg,
+                                                                   const float* __restrict__ mean_density, uint32_t n_rays_global, SamplerBuffers sb, LossBuffers lb) {
+    const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x;
+    const bool active = i < sb.counters[0];
+    uint32_t cn = active ? lb.compacted_numsteps[i] : 0;
+    uint32_t total;
+    const uint32_t cbase = sb.block_steps[blockIdx.x] + block_exclusive_scan(cn, total);
+    if (!active) return;
+    const uint32_t base = sb.numsteps[i * 2 + 1];
+    cn = min(max_compacted - min(max_compacted, cbase), cn);   // :1831-1833
+    sb.numsteps[i * 2 + 0] = cn; sb.numsteps[i * 2 + 1] = cbase;
+    if (cn == 0) return;
+    const float* cin = sb.coords + (size_t)base * 7;
+    const __half* no = lb.network_output + (size_t)base * 4;
+    const float* rs = lb.ray_scratch + (size_t)i * 8;
+    const V3 rgb_ray = ld3(rs), target = ld3(rs + 3);
+    const V3 ray_o = ld3(sb.rays + (size_t)i * 6);
+
+    const LG lg = loss_and_gradient(target, rgb_ray, cfg.loss_type);
+    const float mean_loss = (lg.loss.x + lg.loss.y + lg.loss.z) / 3.0f;
+    if (lb.loss) lb.loss[i] = mean_loss / (float)n_rays_global;
+    const float loss_scale = cfg.loss_scale / (float)n_rays_global;   // :1903
+    const float output_l2_reg = cfg.rgb_activation == ACT_EXPONENTIAL ? 1e-4f : 0.0f;
+    const float output_l1_reg_density = *mean_density < NERF_MIN_OPTICAL_THICKNESS ? 1e-4f : 0.0f;
+
+    V3 rgb_ray2 = v3(0, 0, 0); float T = 1.f;
+    __half* gout = lb.dloss_doutput + (size_t)cbase * 4;
+    float* cout = lb.coords_compacted + (size_t)cbase * 7;
+    for (uint32_t j = 0; j < cn; ++j) {
+        float c[7];
+#pragma unroll
+        for (int k = 0; k < 7; ++k) { c[k] = __ldg(cin + (size_t)j * 7 + k); cout[(size_t)j * 7 + k] = c[k]; }
+        const V3 pos = unwarp_position(v3(c[0], c[1], c[2]), aabb);
+        const float depth = length3(pos - ray_o);
+        const float dt = unwarp_dt(c[3]);
+        float o[4]; load_out4(no + (size_t)j * 4, o);
+        const V3 rgb = v3(network_to_rgb(o[0], cfg.rgb_activation), network_to_rgb(o[1], cfg.rgb_activation), network_to_rgb(o[2], cfg.rgb_activation));
+        const float density = network_to_density(o[3], cfg.density_activation);
+        const float alpha = 1.f - expf(-density * dt);
+        const float weight = alpha * T;
+        rgb_ray2 = rgb_ray2 + weight * rgb;
+        T *= (1.f - alpha);
+        const V3 suffix = rgb_ray - rgb_ray2;
+        const V3 dl_drgb = weight * lg.grad;
+        const float g0 = loss_scale * (dl_drgb.x * network_to_rgb_derivative(o[0], cfg.rgb_activation) + fmaxf(0.0f, output_l2_reg * o[0]));
+        const float g1 = loss_scale * (dl_drgb.y * network_to_rgb_derivative(o[1], cfg.rgb_activation) + fmaxf(0.0f, output_l2_reg * o[1]));
+        const float g2 = loss_scale * (dl_drgb.z * network_to_rgb_derivative(o[2], cfg.rgb_activation) + fmaxf(0.0f, output_l2_reg * o[2]));
+        const float dd = network_to_density_derivative(o[3], cfg.density_activation);
+        const V3 tr = T * rgb - suffix;
+        const float dl_dmlp = dd * (dt * (lg.grad.x * tr.x + lg.grad.y * tr.y + lg.grad.z * tr.z));
+        const float g3 = loss_scale * dl_dmlp + (o[3] < 0.0f ? -output_l1_reg_density : 0.0f) + (o[3] > -10.0f && depth < cfg.near_distance ? 1e-4f : 0.0f);
+        __half2 h[2] = {__floats2half2_rn(g0, g1), __floats2half2_rn(g2, g3)};
+        *reinterpret_cast<uint2*>(gout + (size_t)j * 4) = *reinterpret_cast<uint2*>(h);
+    }
+}
+
+void nerf_compute_loss(cudaStream_t s, uint32_t n_rays, Aabb aabb, uint32_t n_rays_total, Pcg32 rng, uint32_t max_compacted, const LossConfig& cfg,
+                       uint32_t n_images, const ImageMeta* metas, const float* mean_density_dev, uint32_t ray_offset, uint32_t n_rays_global,
+                       const SamplerBuffers& sb, const LossBuffers& lb) {
+    (void)n_rays_total;
+    const uint32_t blocks = div_round_up(n_rays, SCAN_BLOCK);
+    loss_forward_kernel<<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, rng, cfg, n_images, metas, ray_offset, n_rays_global, sb, lb);
+    NGP_POST_LAUNCH();
+    scan_block_totals_kernel<<<1, 1024, 0, s>>>(blocks, sb.block_steps, nullptr, &sb.counters[2], nullptr, false);
+    NGP_POST_LAUNCH();
+    loss_backward_kernel<<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, max_compacted, cfg, mean_density_dev, n_rays_global, sb, lb);
+    NGP_POST_LAUNCH();
+}
+
+// fill_rollover_and_rescale<T> / fill_rollover<T> (tcnn, recalled; testbed_nerf.cu:4061-4069): entries [n_input, n_target) are
+// cyclic copies of [0, n_input); the gradient copies are multiplied by n_input/n_target.
+__global__ void fill_rollover_kernel(uint32_t n_target, const uint32_t* __restrict__ n_input_ptr, __half* __restrict__ dloss, float* __restrict__ coords) {
+    const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x;
+    const uint32_t n_input = min(*n_input_ptr, n_target);
+    if (i < n_input || i >= n_target || n_input == 0) return;
+    const uint32_t src = i % n_input;
+    // element-wise semantics of the reference: element e of the flattened [n x stride] array copies element e % (n_input*stride)
+    const float scale = ((float)n_input * 4.0f) / ((float)n_target * 4.0f);
+    const uint2 raw = *reinterpret_cast<const uint2*>(dloss + (size_t)src * 4);
+    const __half* h = reinterpret_cast<const __half*>(&raw);
+    __half2 o[2] = {__floats2half2_rn(__half2float(h[0]) * scale, __half2float(h[1]) * scale), __floats2half2_rn(__half2float(h[2]) * scale, __half2float(h[3]) * scale)};
+    *reinterpret_cast<uint2*>(dloss + (size_t)i * 4) = *reinterpret_cast<uint2*>(o);
+#pragma unroll
+    for (int k = 0; k < 7; ++k) coords[(size_t)i * 7 + k] = coords[(size_t)src * 7 + k];
+}
+void nerf_fill_rollover(cudaStream_t s, uint32_t n_target, const uint32_t* n_input_dev, __half* dloss, float* coords) {
+    fill_rollover_kernel<<<div_round_up(n_target, 256), 256, 0, s>>>(n_target, n_input_dev, dloss, coords);
+    NGP_POST_LAUNCH();
+}
+
+
+// =================================================================================================================
+// Inference tracer (wavefront): init_rays_with_payload_kernel_nerf (:2228-2352) + advance_pos_nerf (:850-893),
+// compact_kernel_nerf (:2198-2226), generate_next_nerf_network_inputs (:948-1022), composite_kernel_nerf (:1024-1230,
+// Shade mode only), shade_kernel_nerf (:2164-2196).
+// =================================================================================================================
+NGP_D float advance_to_occupied(float t, float cone, V3 o, V3 d, V3 idir, const uint8_t* __restrict__ bitfield, uint32_t min_mip, uint32_t max_mip, const Aabb& aabb) {
+    while (true) {   // if_unoccupied_advance_to_next_occupied_voxel (:811-845)
+        const V3 pos = ray_at(o, d, t);
+        if (t >= MAX_DEPTH || !aabb_contains(aabb, pos)) return MAX_DEPTH;
+        uint32_t mip = (uint32_t)clampi((int)mip_from_pos(pos, NERF_CASCADES - 1), (int)min_mip, (int)max_mip);
+        if (!bitfield || density_grid_occupied_at(pos, bitfield, mip)) return t;
+        while (mip < max_mip && !density_grid_occupied_at(pos, bitfield, mip + 1)) ++mip;
+        t = advance_to_next_voxel(t, cone, pos, d, idir, mip);
+    }
+}
+
+__global__ void init_rays_kernel(RenderCamera cam, uint32_t sample_index, bool snap, Aabb render_aabb, const uint8_t* __restrict__ bitfield,
+                                 uint32_t max_mip, float cone, RaysSoa rays, float* __restrict__ frame_rgba, float* __restrict__ frame_depth) {
+    const uint32_t x = threadIdx.x + blockDim.x * blockIdx.x, yl = threadIdx.y + blockDim.y * blockIdx.y;
+    const uint32_t W = cam.res[0], y = cam.y0 + yl;
+    if (x >= W || y >= (uint32_t)cam.y1) return;
+    const uint32_t local = x + W * yl, idx = x + W * y;
+    float off[2]; ld_random_pixel_offset(snap ? 0 : sample_index, off);
+    const float u = ((float)x + off[0]) / (float)W, v = ((float)y + off[1]) / (float)cam.res[1];
+    V3 o, d; float no_lens[4] = {0, 0, 0, 0};
+    uv_to_ray(cam.camera, cam.res, cam.focal_length, cam.screen_center, LENS_PERSPECTIVE, no_lens, u, v, o, d);
+    NerfPayload& p = rays.payload[local];
+    p.max_weight = 0.0f; p.idx = idx; p.n_steps = 0; p.alive = 0; p.pad = 0;
+    p.origin[0] = o.x; p.origin[1] = o.y; p.origin[2] = o.z;
+    frame_depth[local] = MAX_DEPTH;
+    reinterpret_cast<float4*>(frame_rgba)[local] = make_float4(0, 0, 0, 0);
+    reinterpret_cast<float4*>(rays.rgba)[local] = make_float4(0, 0, 0, 0);
+    rays.depth[local] = 0.0f;
+    d = normalize3(d);
+    p.dir[0] = d.x; p.dir[1] = d.y; p.dir[2] = d.z;
+    float tmin, tmax; aabb_ray_intersect(render_aabb, o, d, tmin, tmax);
+    float t = fmaxf(tmin, 0.0f) + 1e-6f;
+    p.t = t;
+    if (!aabb_contains(render_aabb, ray_at(o, d, t))) return;
+    // advance_pos_nerf: jittered first step, then skip to the first occupied voxel
+    const V3 idir = v3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+    t = advance_n_steps(t, cone, ld_random_val(sample_index, idx * 786433u));
+    t = advance_to_occupied(t, cone, o, d, idir, bitfield, 0, max_mip, render_aabb);
+    if (t >= MAX_DEPTH) return;
+    p.t = t; p.alive = 1;
+}
+
+__global__ void __launch_bounds__(SCAN_BLOCK) compact_count_kernel(uint32_t n, const NerfPayload* __restrict__ payloads, uint32_t* __restrict__ block_alive) {
+    const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x;
+    uint32_t total;
+    block_exclusive_scan((i < n && payloads[i].alive) ? 1u : 0u, total);
+    if (threadIdx.x == 0) block_alive[blockIdx.x] = total;
+}
+__global__ void __launch_bounds__(SCAN_BLOCK) compact_scatter_kernel(uint32_t n, RaysSoa src, RaysSoa dst, RaysSoa hit, const uint32_t* __restrict__ block_alive,
+                                                                     uint32_t* __restrict__ counters) {
+    const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x;
+    const bool in = i < n;
+    const bool alive = in && src.payload[i].alive;
+    uint32_t total;
+    const uint32_t pos = block_alive[blockIdx.x] + block_exclusive_scan(alive ? 1u : 0u, total);
+    if (!in) return;
+    const float4 c = reinterpret_cast<const float4*>(src.rgba)[i];
+    if (alive) {
+        dst.payload[pos] = src.payload[i]; reinterpret_cast<float4*>(dst.rgba)[pos] = c; dst.depth[pos] = src.depth[i];
+    } else if (c.w > 0.001f) {
+        const uint32_t h = atomicAdd(&counters[1], 1u);   // order of finished rays is irrelevant (one pixel each)
+        hit.payload[h] = src.payload[i]; reinterpret_cast<float4*>(hit.rgba)[h] = c; hit.depth[h] = src.depth[i];
+    }
+}
+
+__global__ void next_inputs_kernel(uint32_t n_alive, Aabb render_aabb, Aabb train_aabb, RaysSoa rays, float* __restrict__ input, uint32_t n_steps,
+                                   const uint8_t* __restrict__ bitfield, uint32_t max_mip, float cone) {
+    const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x;
+    if (i >= n_alive) return;
+    NerfPayload& p = rays.payload[i];
+    if (!p.alive) return;
+    const V3 o = ld3(p.origin), d = ld3(p.dir), idir = v3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+    const V3 wd = warp_direction(d);
+    float t = p.t;
+    for (uint32_t j = 0; j < n_steps; ++j) {
+        t = advance_to_occupied(t, cone, o, d, idir, bitfield, 0, max_mip, render_aabb);
+        if (t >= MAX_DEPTH) { p.n_steps = (uint16_t)j; return; }
+        const float dt = calc_dt(t, cone);
+        float* c = input + (size_t)(i + j * n_alive) * 7;
+        const V3 wp = warp_position(ray_at(o, d, t), train_aabb);
+        c[0] = wp.x; c[1] = wp.y; c[2] = wp.z; c[3] = warp_dt(dt); c[4] = wd.x; c[5] = wd.y; c[6] = wd.z;
+        t += dt;
+    }
+    p.t = t; p.n_steps = (uint16_t)n_steps;
+}
+
+__global__ void composite_kernel(uint32_t n_alive, uint32_t current_step, Aabb aabb, const float* __restrict__ camera_dev, float cam_fwd_x, float cam_fwd_y,
+                                 float cam_fwd_z, float cam_x, float cam_y, float cam_z, RaysSoa rays, const float* __restrict__ input,
+                                 const __half* __restrict__ output, uint32_t n_steps, int rgb_act, int density_act, float min_transmittance) {
+    (void)camera_dev;
+    const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x;
+    if (i >= n_alive) return;
+    NerfPayload& p = rays.payload[i];
+    if (!p.alive) return;
+    float4 c = reinterpret_cast<float4*>(rays.rgba)[i];
+    float local_depth = rays.depth[i];
+    const V3 cam_fwd = v3(cam_fwd_x, cam_fwd_y, cam_fwd_z), cam_pos = v3(cam_x, cam_y, cam_z);
+    const uint32_t actual = p.n_steps;
+    uint32_t j = 0;
+    for (; j < actual; ++j) {
+        float o[4]; load_out4(output + (size_t)(i + j * n_alive) * 4, o);
+        const float* in = input + (size_t)(i + j * n_alive) * 7;
+        const V3 pos = unwarp_position(v3(in[0], in[1], in[2]), aabb);
+        const float T = 1.f - c.w;
+        const float dt = unwarp_dt(in[3]);
+        const float alpha = 1.f - expf(-network_to_density(o[3], density_act) * dt);
+        const float weight = alpha * T;
+        c.x += network_to_rgb(o[0], rgb_act) * weight; c.y += network_to_rgb(o[1], rgb_act) * weight; c.z += network_to_rgb(o[2], rgb_act) * weight;
+        c.w += weight;
+        if (weight > p.max_weight) { p.max_weight = weight; local_depth = dot3(cam_fwd, pos - cam_pos); }
+        if (c.w > (1.0f - min_transmittance)) { const float a = c.w; c.x /= a; c.y /= a; c.z /= a; c.w /= a; break; }
+    }
+    if (j < n_steps) { p.alive = 0; p.n_steps = (uint16_t)(j + current_step); }
+    reinterpret_cast<float4*>(rays.rgba)[i] = c;
+    rays.depth[i] = local_depth;
+}
+
+__global__ void shade_kernel(uint32_t n_hit, RaysSoa hit, bool linear_colors, uint32_t idx_offset, float* __restrict__ frame_rgba, float* __restrict__ frame_depth) {
+    const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x;
+    if (i >= n_hit) return;
+    float4 t = reinterpret_cast<const float4*>(hit.rgba)[i];
+    if (!linear_colors) { t.x = srgb_to_linear(t.x); t.y = srgb_to_linear(t.y); t.z = srgb_to_linear(t.z); }   // accumulate in linear colours
+    const uint32_t local = hit.payload[i].idx - idx_offset;
+    const float4 f = reinterpret_cast<const float4*>(frame_rgba)[local];
+    reinterpret_cast<float4*>(frame_rgba)[local] = make_float4(t.x + f.x * (1.0f - t.w), t.y + f.y * (1.0f - t.w), t.z + f.z * (1.0f - t.w), t.w + f.w * (1.0f - t.w));
+    if (t.w > 0.2f) frame_depth[local] = hit.depth[i];
+}
+
+void nerf_init_rays(cudaStream_t s, const RenderCamera& cam, uint32_t sample_index, bool snap, Aabb render_aabb, const uint8_t* bitfield,
+                    uint32_t max_mip, float cone, RaysSoa rays, float* frame_rgba, float* frame_depth) {
+    const dim3 threads = {16, 8, 1};
+    const dim3 blocks = {div_round_up((uint32_t)cam.res[0], 16), div_round_up((uint32_t)(cam.y1 - cam.y0), 8), 1};
+    init_rays_kernel<<<blocks, threads, 0, s>>>(cam, sample_index, snap, render_aabb, bitfield, max_mip, cone, rays, frame_rgba, frame_depth);
+    NGP_POST_LAUNCH();
+}
+void nerf_compact_rays(cudaStream_t s, uint32_t n, RaysSoa src, RaysSoa dst, RaysSoa hit, uint32_t* counters, uint32_t* scan_scratch) {
+    const uint32_t blocks = div_round_up(n, SCAN_BLOCK);
+    compact_count_kernel<<<blocks, SCAN_BLOCK, 0, s>>>(n, src.payload, scan_scratch); NGP_POST_LAUNCH();
+    scan_block_totals_kernel<<<1, 1024, 0, s>>>(blocks, scan_scratch, nullptr, &counters[0], nullptr, false); NGP_POST_LAUNCH();
+    compact_scatter_kernel<<<blocks, SCAN_BLOCK, 0, s>>>(n, src, dst, hit, scan_scratch, counters); NGP_POST_LAUNCH();
+}
+void nerf_generate_next_inputs(cudaStream_t s, uint32_t n_alive, Aabb render_aabb, Aabb train_aabb, RaysSoa rays, float* input, uint32_t n_steps,
+                               const uint8_t* bitfield, uint32_t max_mip, float cone) {
+    next_inputs_kernel<<<div_round_up(n_alive, 128), 128, 0, s>>>(n_alive, render_aabb, train_aabb, rays, input, n_steps, bitfield, max_mip, cone);
+    NGP_POST_LAUNCH();
+}
+void nerf_composite(cudaStream_t s, uint32_t n_alive, uint32_t current_step, Aabb train_aabb, const float* camera, RaysSoa rays, const float* input,
+                    const __half* output, uint32_t n_steps, int rgb_act, int density_act, float min_transmittance) {
+    composite_kernel<<<div_round_up(n_alive, 128), 128, 0, s>>>(n_alive, current_step, train_aabb, nullptr, camera[6], camera[7], camera[8], camera[9], camera[10],
+                                                                camera[11], rays, input, output, n_steps, rgb_act, density_act, min_transmittance);
+    NGP_POST_LAUNCH();
+}
+void nerf_shade(cudaStream_t s, uint32_t n_hit, RaysSoa hit, bool linear_colors, uint32_t idx_offset, float* frame_rgba, float* frame_depth) {
+    if (n_hit == 0) return;
+    shade_kernel<<<div_round_up(n_hit, 128), 128, 0, s>>>(n_hit, hit, linear_colors, idx_offset, frame_rgba, frame_depth);
+    NGP_POST_LAUNCH();
+}
+
+}  // namespace ngp

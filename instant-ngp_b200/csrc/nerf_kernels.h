@@ -1,0 +1,80 @@
+// Launchers of the NeRF-specific kernels (sampler, occupancy grid, loss/compositor, inference tracer).
+// Reference: src/testbed_nerf.cu (kernel-by-kernel citations in nerf_kernels.cu).
+#pragma once
+#include "nerf_device.cuh"
+
+namespace ngp {
+
+// ---- occupancy grid (testbed_nerf.cu:503-592,635-809,3412-3567) ----
+void nerf_mark_untrained_grid(cudaStream_t s, uint32_t n_elements, float* grid, uint32_t n_images, const ImageMeta* metas, bool clear_visible);
+void nerf_generate_grid_samples(cudaStream_t s, uint32_t n, Pcg32 rng, uint32_t step, Aabb aabb, const float* grid_in, float* pos_out,
+                                uint32_t* indices, uint32_t n_cascades, float thresh);
+void nerf_splat_grid_samples(cudaStream_t s, uint32_t n, const uint32_t* indices, const __half* density_raw, float* grid_tmp, int density_activation);
+void nerf_ema_grid(cudaStream_t s, uint32_t n_elements, float decay, float* grid, const float* grid_tmp);
+// mean over cascade 0 (deterministic two-stage reduction) -> *mean_dev ; bitfield + 7 OR-pooled mips
+void nerf_update_bitfield(cudaStream_t s, const float* grid, uint32_t n_cascades, uint8_t* bitfield, float* mean_dev, float* partials /* [1024] */);
+
+// ---- training sampler (testbed_nerf.cu:1382-1658), deterministic ray-order compaction ----
+struct SamplerBuffers {
+    // per generated ray slot [n_rays]
+    uint32_t* numsteps_all;     // pass-1 step count of ray i (0: no sample / masked)
+    uint32_t* block_steps;      // [n_blocks] per-block totals -> exclusive prefix after the scan
+    uint32_t* block_rays;       // [n_blocks]
+    float* ray_tmp;             // [n_rays][8]: o(3), d unnormalised(3), startt, cone_angle (pass 1 -> pass 2)
+    // compacted outputs
+    uint32_t* ray_indices;      // [n_rays]
+    float* rays;                // [n_rays][6] unnormalised o,d
+    uint32_t* numsteps;         // [n_rays][2] (numsteps, base)
+    float* coords;              // [max_samples][7]
+    uint32_t* counters;         // [0] ray_counter, [1] numsteps_counter (total, may exceed max_samples), [2] compacted counter
+};
+void nerf_generate_training_samples(cudaStream_t s, uint32_t n_rays, Aabb aabb, uint32_t max_samples, uint32_t n_rays_total, Pcg32 rng,
+                                    uint32_t n_images, const ImageMeta* metas, const uint8_t* bitfield, uint32_t max_mip,
+                                    bool snap_to_pixel_centers, float cone_angle_constant, uint32_t ray_offset, uint32_t n_rays_global,
+                                    const SamplerBuffers& b);
+
+// ---- loss + compositor + gradient (testbed_nerf.cu:1660-2012) ----
+struct LossConfig {
+    int loss_type, rgb_activation, density_activation;
+    int random_bg_color, linear_colors, snap_to_pixel_centers;
+    float background_color[3];
+    float loss_scale;       // LOSS_SCALE; divided by the (global) ray count inside
+    float near_distance;
+};
+struct LossBuffers {
+    const __half* network_output;   // [*][4]
+    __half* dloss_doutput;          // [max_compacted][4]
+    float* coords_compacted;        // [max_compacted][7]
+    float* loss;                    // [n_rays]
+    float* ray_scratch;             // [n_rays][8]: rgb_ray(3), target(3), spare
+    uint32_t* compacted_numsteps;   // [n_rays] pass-1 compacted step counts
+};
+void nerf_compute_loss(cudaStream_t s, uint32_t n_rays, Aabb aabb, uint32_t n_rays_total, Pcg32 rng, uint32_t max_samples_compacted,
+                       const LossConfig& cfg, uint32_t n_images, const ImageMeta* metas, const float* mean_density_dev,
+                       uint32_t ray_offset, uint32_t n_rays_global, const SamplerBuffers& sb, const LossBuffers& lb);
+// fill_rollover_and_rescale + fill_rollover (tcnn; testbed_nerf.cu:4061-4069) on dL [n_target][4] fp16 and coords [n_target][7]
+void nerf_fill_rollover(cudaStream_t s, uint32_t n_target, const uint32_t* n_input_dev, __half* dloss, float* coords);
+// sum of loss[0..n) -> *out_dev (deterministic)
+void reduce_sum_f32(cudaStream_t s, const float* in, uint32_t n, float* out_dev, float* partials /* [1024] */);
+
+// ---- inference tracer (testbed_nerf.cu:850-1230,2164-2352,2417-2693) ----
+struct NerfPayload {   // nerf.h:32-40
+    float origin[3]; float dir[3]; float t; float max_weight; uint32_t idx; uint16_t n_steps; uint8_t alive; uint8_t pad;
+};
+struct RaysSoa { float* rgba; float* depth; NerfPayload* payload; };   // rgba [n][4]
+struct RenderCamera {
+    int res[2]; float focal_length[2]; float screen_center[2]; float camera[12];
+    int y0, y1;     // row band rendered by this call (tile sharding); ray index = x + W*(y - y0)
+};
+void nerf_init_rays(cudaStream_t s, const RenderCamera& cam, uint32_t sample_index, bool snap_to_pixel_centers, Aabb render_aabb,
+                    const uint8_t* bitfield, uint32_t max_mip, float cone_angle, RaysSoa rays, float* frame_rgba, float* frame_depth);
+// alive -> dst (compacted, order preserving), finished with alpha > 0.001 -> hit ; counters[0] = n_alive, counters[1] += n_hit
+void nerf_compact_rays(cudaStream_t s, uint32_t n, RaysSoa src, RaysSoa dst, RaysSoa hit, uint32_t* counters, uint32_t* scan_scratch);
+void nerf_generate_next_inputs(cudaStream_t s, uint32_t n_alive, Aabb render_aabb, Aabb train_aabb, RaysSoa rays, float* network_input /*[n_alive*k][7]*/,
+                               uint32_t n_steps, const uint8_t* bitfield, uint32_t max_mip, float cone_angle);
+void nerf_composite(cudaStream_t s, uint32_t n_alive, uint32_t current_step, Aabb train_aabb, const float* camera, RaysSoa rays,
+                    const float* network_input, const __half* network_output, uint32_t n_steps, int rgb_activation, int density_activation,
+                    float min_transmittance);
+void nerf_shade(cudaStream_t s, uint32_t n_hit, RaysSoa hit, bool linear_colors, uint32_t idx_offset, float* frame_rgba, float* frame_depth);
+
+}  // namespace ngp

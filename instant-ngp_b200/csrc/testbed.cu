@@ -1,0 +1,358 @@
+// Host driver (see testbed.h).  Control flow mirrors Testbed::train / train_nerf / train_nerf_step /
+// update_density_grid_nerf / train_image of the reference; the kernels are the sm_100a ones of this library.
+#include "testbed.h"
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+namespace ngp {
+
+static int loss_type_from_string(const std::string& s) {   // string_to_loss_type (testbed.cu:3872-3891)
+    const std::string l = to_lower(s);
+    if (l == "l2") return LOSS_L2; if (l == "l1") return LOSS_L1; if (l == "mape") return LOSS_MAPE; if (l == "smape") return LOSS_SMAPE;
+    if (l == "huber" || l == "smoothl1") return LOSS_HUBER; if (l == "logl1") return LOSS_LOGL1; if (l == "relativel2") return LOSS_RELL2;
+    throw Error("Unknown loss type '" + s + "'");
+}
+
+Testbed::Testbed(int mode) : m_mode(mode), m_rng(1337), m_density_grid_rng(1337) {
+    NGP_CHECK(mode == MODE_TB_NERF || mode == MODE_TB_IMAGE, "Testbed: only the Nerf and Image modes are implemented on this path");
+}
+
+Testbed::~Testbed() { for (void* p : m_image_buffers) cudaFree(p); }
+
+void Testbed::reload_network_from_json(const std::string& json) {
+    Json patch = Json::parse(json);
+    if (m_have_config && patch.contains("parent")) m_config.merge_patch(patch); else m_config = patch;   // "parent" merge: testbed.cu:95-106
+    m_have_config = true;
+    reset_network();
+}
+
+// reset_network (testbed.cu:3903-4151): seeds, counters, network + trainer construction, parameter init
+void Testbed::reset_network() {
+    m_rng = Pcg32(seed);                       // testbed.cu:3906
+    m_density_grid_rng = Pcg32(m_rng.next_uint());   // testbed.cu:3919 (density_grid_rng seeded from m_rng)
+    m_training_step = 0; m_loss_scalar = 0.f;
+    m_rays_per_batch = 1u << 12; m_n_rays_total = 0; m_measured = 0; m_measured_before = 0;   // testbed.cu:3912, testbed.h:440
+    m_density_grid_ema_step = 0;
+    const Json& opt = m_config.contains("optimizer") ? m_config.at("optimizer") : Json::parse("{\"otype\":\"Adam\"}");
+    if (m_mode == MODE_TB_NERF) {
+        if (m_config.contains("loss")) loss_type = loss_type_from_string(m_config.at("loss").value("otype", "L2"));   // testbed.cu:3953-3956
+        m_nerf_net = std::make_unique<NerfNetwork>(m_config);
+        m_trainer = std::make_unique<Trainer>(m_nerf_net->n_params, m_nerf_net->n_matrix_params, opt);
+        m_nerf_net->initialize_params(seed, m_trainer->master, 0);
+        if (m_grid_allocated) {
+            NGP_CUDA_CHECK(cudaMemset(m_density_grid.ptr, 0, m_density_grid.bytes));
+            NGP_CUDA_CHECK(cudaMemset(m_bitfield.ptr, 0, m_bitfield.bytes));
+        }
+    } else {
+        m_image_net = std::make_unique<EncodedMlp>(m_config, 2, 3);
+        m_trainer = std::make_unique<Trainer>(m_image_net->n_params, m_image_net->n_matrix_params, opt);
+        m_image_net->initialize_params(seed, m_trainer->master, 0);
+    }
+    m_trainer->params_from_master(0);
+    NGP_CUDA_CHECK(cudaDeviceSynchronize());
+}
+
+// NerfDataset upload + load_nerf_post (testbed_nerf.cu:3046-3112): aabb, cascades, cone angle
+void Testbed::set_nerf_dataset(cudaStream_t s, uint32_t n_images, const HostImage* images, int aabb_scale) {
+    NGP_CHECK(m_mode == MODE_TB_NERF, "set_nerf_dataset: testbed is not in Nerf mode");
+    NGP_CHECK(n_images > 0 && images, "set_nerf_dataset: no images");
+    NGP_CHECK(aabb_scale >= 1 && (aabb_scale & (aabb_scale - 1)) == 0, "NeRF dataset's `aabb_scale` must be a power of two");
+    NGP_CHECK(aabb_scale <= (1 << (NERF_CASCADES - 1)), "NeRF dataset must have `aabb_scale <= 128`");
+    for (void* p : m_image_buffers) cudaFree(p);
+    m_image_buffers.clear();
+    std::vector<ImageMeta> metas(n_images);
+    for (uint32_t i = 0; i < n_images; ++i) {
+        const HostImage& h = images[i];
+        NGP_CHECK(h.data_type == IMG_BYTE || h.data_type == IMG_FLOAT, "image data type must be RGBA8 (0) or RGBA float32 (1)");
+        NGP_CHECK(h.lens_mode == LENS_PERSPECTIVE || h.lens_mode == LENS_OPENCV, "lens mode must be Perspective (0) or OpenCV (1)");
+        const size_t bytes = (size_t)h.res[0] * h.res[1] * (h.data_type == IMG_BYTE ? 4 : 16);
+        void* d = nullptr;
+        NGP_CUDA_CHECK(cudaMalloc(&d, bytes));
+        m_image_buffers.push_back(d);
+        NGP_CUDA_CHECK(cudaMemcpyAsync(d, h.pixels, bytes, cudaMemcpyHostToDevice, s));
+        ImageMeta& m = metas[i];
+        m.pixels = d; m.data_type = h.data_type; m.lens_mode = h.lens_mode;
+        memcpy(m.lens_params, h.lens_params, sizeof(m.lens_params)); memcpy(m.res, h.res, sizeof(m.res));
+        memcpy(m.principal_point, h.principal_point, sizeof(m.principal_point)); memcpy(m.focal_length, h.focal_length, sizeof(m.focal_length));
+        memcpy(m.xform, h.xform, sizeof(m.xform));
+    }
+    ImageMeta* md = m_metas.get<ImageMeta>(n_images);
+    NGP_CUDA_CHECK(cudaMemcpyAsync(md, metas.data(), n_images * sizeof(ImageMeta), cudaMemcpyHostToDevice, s));
+    NGP_CUDA_CHECK(cudaStreamSynchronize(s));
+    m_n_images = n_images; m_aabb_scale = aabb_scale;
+    const float half = 0.5f * (float)std::min(1 << (NERF_CASCADES - 1), aabb_scale);   // m_aabb.inflate(0.5 * aabb_scale) around 0.5
+    for (int k = 0; k < 3; ++k) { aabb.min[k] = 0.5f - half; aabb.max[k] = 0.5f + half; }
+    render_aabb = aabb;
+    m_max_cascade = 0;
+    while ((1 << m_max_cascade) < aabb_scale) ++m_max_cascade;
+    cone_angle_constant = aabb_scale <= 1 ? 0.0f : (1.0f / 256.0f);   // testbed_nerf.cu:3109
+    // density grid: always all 8 mips of bitfield (testbed_nerf.cu:3541-3542)
+    const size_t n_elements = (size_t)NERF_GRID_N_CELLS * (m_max_cascade + 1);
+    NGP_CUDA_CHECK(cudaMemsetAsync(m_density_grid.get<float>(n_elements), 0, n_elements * 4, s));
+    m_density_grid_tmp.get<float>(n_elements);
+    NGP_CUDA_CHECK(cudaMemsetAsync(m_bitfield.get<uint8_t>((size_t)NERF_GRID_N_CELLS * NERF_CASCADES / 8), 0, (size_t)NERF_GRID_N_CELLS * NERF_CASCADES / 8, s));
+    NGP_CUDA_CHECK(cudaMemsetAsync(m_mean.get<float>(4), 0, 16, s));
+    m_partials.get<float>(1024);
+    m_grid_pos.get<float>(n_elements * 3); m_grid_idx.get<uint32_t>(n_elements); m_grid_out.get<__half>(n_elements);
+    m_grid_allocated = true;
+    m_training_step = 0; m_density_grid_ema_step = 0;
+    NGP_CUDA_CHECK(cudaStreamSynchronize(s));
+}
+
+void Testbed::set_image(cudaStream_t s, const float* rgba_host, int w, int h) {
+    NGP_CHECK(m_mode == MODE_TB_IMAGE, "set_image: testbed is not in Image mode");
+    NGP_CHECK(rgba_host && w > 1 && h > 1, "set_image: bad image");
+    NGP_CUDA_CHECK(cudaMemcpyAsync(m_image.get<float>((size_t)w * h * 4), rgba_host, (size_t)w * h * 16, cudaMemcpyHostToDevice, s));
+    NGP_CUDA_CHECK(cudaStreamSynchronize(s));
+    m_image_w = w; m_image_h = h;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// update_density_grid_nerf (testbed_nerf.cu:3412-3536) + training_prep_nerf (:4137-4152)
+// ---------------------------------------------------------------------------------------------------------------
+void Testbed::update_density_grid_nerf(cudaStream_t s, float decay, uint32_t n_uniform, uint32_t n_nonuniform) {
+    const uint32_t n_cascades = m_max_cascade + 1;
+    const uint32_t n_elements = NERF_GRID_N_CELLS * n_cascades;
+    const uint32_t n_samples = n_uniform + n_nonuniform;
+    float* grid = m_density_grid.as<float>(); float* tmp = m_density_grid_tmp.as<float>();
+    float* pos = m_grid_pos.as<float>(); uint32_t* idx = m_grid_idx.as<uint32_t>(); __half* out = m_grid_out.as<__half>();
+    if (m_training_step == 0) {
+        m_density_grid_ema_step = 0;
+        nerf_mark_untrained_grid(s, n_elements, grid, m_n_images, m_metas.as<ImageMeta>(), true);
+    }
+    NGP_CUDA_CHECK(cudaMemsetAsync(tmp, 0, sizeof(float) * n_elements, s));
+    nerf_generate_grid_samples(s, n_uniform, m_density_grid_rng, m_density_grid_ema_step, aabb, grid, pos, idx, n_cascades, -0.01f);
+    m_density_grid_rng.advance();
+    nerf_generate_grid_samples(s, n_nonuniform, m_density_grid_rng, m_density_grid_ema_step, aabb, grid, pos + (size_t)n_uniform * 3, idx + n_uniform, n_cascades,
+                               NERF_MIN_OPTICAL_THICKNESS);
+    m_density_grid_rng.advance();
+    // density() on the TRAINING params (use_inference_params = false, :3514), chunks of 2*128^3
+    for (uint32_t i = 0; i < n_samples; i += NERF_GRID_N_CELLS * 2) {
+        const uint32_t batch = std::min(NERF_GRID_N_CELLS * 2, n_samples - i);
+        m_nerf_net->density(s, m_trainer->params, pos + (size_t)i * 3, 3, batch, out + i);
+    }
+    nerf_splat_grid_samples(s, n_samples, idx, out, tmp, density_activation);
+    nerf_ema_grid(s, n_elements, decay, grid, tmp);
+    ++m_density_grid_ema_step;
+    nerf_update_bitfield(s, grid, n_cascades, m_bitfield.as<uint8_t>(), m_mean.as<float>(), m_partials.as<float>());
+}
+
+void Testbed::training_prep_nerf(cudaStream_t s) {
+    const uint32_t n_cascades = m_max_cascade + 1;
+    if (m_training_step < 256) update_density_grid_nerf(s, density_grid_decay, NERF_GRID_N_CELLS * n_cascades, 0);
+    else update_density_grid_nerf(s, density_grid_decay, NERF_GRID_N_CELLS / 4 * n_cascades, NERF_GRID_N_CELLS / 4 * n_cascades);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Testbed::train (testbed.cu:4285-4370)
+// ---------------------------------------------------------------------------------------------------------------
+void Testbed::train(cudaStream_t s, uint32_t batch_size) { train_begin(s, batch_size); train_end(s, 0, 0); }
+
+void Testbed::train_begin(cudaStream_t s, uint32_t batch_size) {
+    NGP_CHECK(m_trainer, "Cannot train without a network: call reload_network_from_json first");
+    NGP_CHECK(batch_size >= BATCH_GRANULARITY && batch_size % BATCH_GRANULARITY == 0, "training batch size must be a multiple of 256");
+    if (m_mode == MODE_TB_NERF) {
+        NGP_CHECK(m_n_images > 0, "Cannot train without training data");
+        const uint32_t n_prep_to_skip = std::min(std::max(m_training_step / 16u, 1u), 16u);
+        if (m_training_step % n_prep_to_skip == 0) training_prep_nerf(s);
+    }
+    // optimizer->update_hyperparams (testbed.cu:4339-4346)
+    m_trainer->opt.optimize_matrix = shall_train_network; m_trainer->opt.optimize_non_matrix = shall_train_encoding;
+    m_get_loss = m_training_step % 16 == 0;
+    m_pending_batch = batch_size;
+    if (m_mode == MODE_TB_NERF) train_nerf_step(s, batch_size);
+    else train_image_step(s, batch_size, m_get_loss);
+}
+
+void Testbed::train_end(cudaStream_t s, uint32_t measured_override, uint32_t measured_before_override) {
+    NGP_CHECK(m_pending_batch > 0, "train_end without train_begin");
+    const uint32_t target = m_pending_batch; m_pending_batch = 0;
+    m_trainer->optimizer_step(s, LOSS_SCALE);   // testbed_nerf.cu:3678 / testbed_image.cu:283
+    ++m_training_step;
+    if (m_mode == MODE_TB_IMAGE) {
+        if (m_get_loss) { NGP_CUDA_CHECK(cudaMemcpyAsync(&m_loss_scalar, m_loss_sum.as<float>(), 4, cudaMemcpyDeviceToHost, s)); }
+        NGP_CUDA_CHECK(cudaStreamSynchronize(s));
+        return;
+    }
+    // NerfCounters::update_after_training (testbed_nerf.cu:3583-3609): two counters (+ the loss every 16 steps) read back
+    if (m_get_loss) reduce_sum_f32(s, m_loss.as<float>(), m_rays_per_batch, m_loss_sum.as<float>(), m_partials.as<float>());
+    uint32_t c[4] = {0, 0, 0, 0}; float loss_sum = 0.f;
+    NGP_CUDA_CHECK(cudaMemcpyAsync(c, m_counters.as<uint32_t>(), sizeof(c), cudaMemcpyDeviceToHost, s));
+    if (m_get_loss) NGP_CUDA_CHECK(cudaMemcpyAsync(&loss_sum, m_loss_sum.as<float>(), 4, cudaMemcpyDeviceToHost, s));
+    NGP_CUDA_CHECK(cudaStreamSynchronize(s));
+    m_measured_before = measured_before_override ? measured_before_override : c[1];
+    m_measured = measured_override ? measured_override : c[2];
+    if (m_measured_before == 0 || m_measured == 0) {
+        m_measured = m_measured_before = 0; m_loss_scalar = 0.f;
+        throw Error("Nerf training generated 0 samples. Aborting training.");   // testbed_nerf.cu:3693-3697
+    }
+    if (m_get_loss) m_loss_scalar = loss_sum * (float)m_measured / (float)target;
+    m_rays_per_batch = (uint32_t)((float)m_rays_per_batch * (float)target / (float)m_measured);
+    m_rays_per_batch = std::min((uint32_t)next_multiple(m_rays_per_batch, BATCH_GRANULARITY), 1u << 18);
+}
+
+TrainStats Testbed::stats() const {
+    TrainStats st{};
+    st.training_step = m_training_step; st.loss = m_loss_scalar; st.rays_per_batch = m_rays_per_batch; st.measured_batch_size = m_measured;
+    st.measured_batch_size_before_compaction = m_measured_before; st.n_rays_total = m_n_rays_total;
+    st.learning_rate = m_trainer ? m_trainer->opt.current_lr : 0.f;
+    st.density_grid_mean = 0.f;
+    return st;
+}
+
+
+// ---------------------------------------------------------------------------------------------------------------
+// train_nerf_step (testbed_nerf.cu:3867-4132)
+// ---------------------------------------------------------------------------------------------------------------
+void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
+    const uint32_t max_samples = target * 16;   // "somewhat of a worst case" (:3873)
+    const uint32_t R = m_rays_per_batch, max_rays = 1u << 18;
+    const uint32_t max_blocks = div_round_up(max_rays, 256);
+    SamplerBuffers sb{};
+    sb.numsteps_all = m_numsteps_all.get<uint32_t>(max_rays); sb.block_steps = m_block_steps.get<uint32_t>(max_blocks);
+    sb.block_rays = m_block_rays.get<uint32_t>(max_blocks); sb.ray_tmp = m_ray_tmp.get<float>((size_t)max_rays * 8);
+    sb.ray_indices = m_ray_indices.get<uint32_t>(max_rays); sb.rays = m_rays.get<float>((size_t)max_rays * 6);
+    sb.numsteps = m_numsteps.get<uint32_t>((size_t)max_rays * 2);
+    const bool fresh_coords = m_coords.bytes < (size_t)max_samples * 7 * 4;
+    sb.coords = m_coords.get<float>((size_t)max_samples * 7);
+    if (fresh_coords) NGP_CUDA_CHECK(cudaMemsetAsync(sb.coords, 0, (size_t)max_samples * 7 * 4, s));   // stale rows are fed to the network: keep them finite
+    sb.counters = m_counters.get<uint32_t>(4);
+    LossBuffers lb{};
+    __half* mlp_out = m_mlp_out.get<__half>((size_t)max_samples * 4);
+    lb.network_output = mlp_out; lb.dloss_doutput = m_dloss.get<__half>((size_t)target * 4);
+    lb.coords_compacted = m_coords_compacted.get<float>((size_t)target * 7); lb.loss = m_loss.get<float>(max_rays);
+    lb.ray_scratch = m_ray_scratch.get<float>((size_t)max_rays * 8); lb.compacted_numsteps = m_compacted_numsteps.get<uint32_t>(max_rays);
+    m_loss_sum.get<float>(4);
+
+    uint32_t max_inference;
+    if (m_measured_before == 0) { m_measured_before = max_inference = max_samples; }
+    else max_inference = (uint32_t)next_multiple(std::min(m_measured_before, max_samples), BATCH_GRANULARITY);
+    if (m_training_step == 0) m_n_rays_total = 0;
+    const uint32_t n_rays_total = m_n_rays_total;
+    m_n_rays_total += R;
+
+    // prepare_for_training_steps (:3569-3581)
+    NGP_CUDA_CHECK(cudaMemsetAsync(sb.counters, 0, 16, s));
+    NGP_CUDA_CHECK(cudaMemsetAsync(lb.loss, 0, sizeof(float) * R, s));
+
+    const uint32_t ray_offset = m_rank * R, n_rays_global = m_world * R;
+    nerf_generate_training_samples(s, R, aabb, max_inference, n_rays_total, m_rng, m_n_images, m_metas.as<ImageMeta>(), m_bitfield.as<uint8_t>(), m_max_cascade,
+                                   snap_to_pixel_centers, cone_angle_constant, ray_offset, n_rays_global, sb);
+    m_nerf_net->inference(s, m_trainer->params, sb.coords, max_inference, mlp_out);   // inference_mixed_precision(.., use_inference_params=false) (:4001)
+
+    LossConfig lc{};
+    lc.loss_type = loss_type; lc.rgb_activation = rgb_activation; lc.density_activation = density_activation;
+    lc.random_bg_color = random_bg_color; lc.linear_colors = linear_colors; lc.snap_to_pixel_centers = snap_to_pixel_centers;
+    memcpy(lc.background_color, background_color, sizeof(lc.background_color));
+    lc.loss_scale = LOSS_SCALE; lc.near_distance = near_distance;
+    nerf_compute_loss(s, R, aabb, n_rays_total, m_rng, target, lc, m_n_images, m_metas.as<ImageMeta>(), m_mean.as<float>(), ray_offset, n_rays_global, sb, lb);
+    nerf_fill_rollover(s, target, &sb.counters[2], lb.dloss_doutput, lb.coords_compacted);   // :4061-4069
+    // forward(compacted) + backward(EGradientMode::Overwrite) (:4077-4078)
+    m_nerf_net->forward_backward(s, m_trainer->params, lb.coords_compacted, target, lb.dloss_doutput, m_trainer->grads);
+    m_rng.advance();   // :4127
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// train_image (testbed_image.cu:214-285): Trainer::training_step = forward + L2 loss + backward
+// ---------------------------------------------------------------------------------------------------------------
+void Testbed::train_image_step(cudaStream_t s, uint32_t n, bool get_loss) {
+    NGP_CHECK(m_image_w > 0, "Cannot train without training data");
+    float* pos = m_img_pos.get<float>((size_t)n * 2); float* target = m_img_target.get<float>((size_t)n * 3);
+    __half* out = m_img_out.get<__half>((size_t)n * 16); __half* dl = m_img_dl.get<__half>((size_t)n * 16);
+    float* lossv = m_img_loss.get<float>(n); m_loss_sum.get<float>(4); m_partials.get<float>(1024);
+    image_generate_batch(s, n, m_rng, image_stratified, m_image.as<float>(), m_image_w, m_image_h, image_snap_to_pixel_centers, image_linear_colors, pos, target);
+    m_rng.advance();
+    m_image_net->inference(s, m_trainer->params, pos, 2, n, out);
+    l2_loss(s, n, out, target, LOSS_SCALE, dl, get_loss ? lossv : nullptr);
+    if (get_loss) reduce_sum_f32(s, lossv, n, m_loss_sum.as<float>(), m_partials.as<float>());
+    m_image_net->forward_backward(s, m_trainer->params, pos, 2, n, dl, m_trainer->grads);
+}
+
+// compute_image_mse (testbed_image.cu:465-527): all pixels at pixel centres, inference params, chunks of 2^20
+float Testbed::compute_image_mse(cudaStream_t s, bool quantize) {
+    NGP_CHECK(m_mode == MODE_TB_IMAGE && m_image_w > 0 && m_trainer, "compute_image_mse needs an image and a network");
+    const uint32_t n_elements = (uint32_t)m_image_w * m_image_h, max_batch = 1u << 20;
+    DeviceBuffer se_buf, pos_buf, tgt_buf, out_buf;
+    float* se = se_buf.get<float>(n_elements + max_batch); float* pos = pos_buf.get<float>((size_t)max_batch * 2);
+    float* tgt = tgt_buf.get<float>((size_t)max_batch * 3); __half* out = out_buf.get<__half>((size_t)max_batch * 16);
+    m_loss_sum.get<float>(4); m_partials.get<float>(1024);
+    for (uint32_t offset = 0; offset < n_elements; offset += max_batch) {
+        const uint32_t batch = (std::min(max_batch, n_elements - offset) + 255u) & ~255u;
+        image_eval_coords(s, batch, offset, m_image.as<float>(), m_image_w, m_image_h, image_linear_colors, pos, tgt);
+        m_image_net->inference(s, m_trainer->inference_params, pos, 2, batch, out);
+        image_squared_error(s, batch, tgt, out, se + offset, quantize);
+    }
+    reduce_sum_f32(s, se, n_elements, m_loss_sum.as<float>(), m_partials.as<float>());
+    float sum = 0.f;
+    NGP_CUDA_CHECK(cudaMemcpyAsync(&sum, m_loss_sum.as<float>(), 4, cudaMemcpyDeviceToHost, s));
+    NGP_CUDA_CHECK(cudaStreamSynchronize(s));
+    return sum / (float)n_elements;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// render_nerf + NerfTracer::trace (testbed_nerf.cu:2417-2693,2752-2871), Shade mode, headless float4 buffer
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void accumulate_kernel(uint32_t n, const float* __restrict__ frame, float* __restrict__ accum, float w_new) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) accum[i] = accum[i] * (1.0f - w_new) + frame[i] * w_new;
+}
+
+void Testbed::render(cudaStream_t s, const float* camera_matrix, const float* focal_length, const float* screen_center, int w, int h, int spp, int y0, int y1,
+                     float* rgba_out, bool out_is_device, float* depth_out) {
+    NGP_CHECK(m_mode == MODE_TB_NERF && m_nerf_net && m_trainer, "render: NeRF network not initialised");
+    NGP_CHECK(w > 0 && h > 0 && y0 >= 0 && y1 <= h && y0 < y1 && spp >= 1, "render: bad resolution / row band");
+    const uint32_t n_pixels = (uint32_t)w * (uint32_t)(y1 - y0);
+    const uint32_t n_pad = (uint32_t)next_multiple(n_pixels, BATCH_GRANULARITY);
+    RaysSoa rays[3];
+    for (int k = 0; k < 3; ++k) rays[k] = {m_r_rgba[k].get<float>((size_t)n_pad * 4), m_r_depth[k].get<float>(n_pad), m_r_payload[k].get<NerfPayload>(n_pad)};
+    constexpr uint32_t MAX_STEPS = 8, MIN_STEPS = 1, MARCH_ITER = 10000;   // :97-100
+    float* input = m_r_input.get<float>((size_t)n_pad * MAX_STEPS * 7); __half* output = m_r_output.get<__half>((size_t)n_pad * MAX_STEPS * 4);
+    uint32_t* counters = m_r_counters.get<uint32_t>(4); uint32_t* scan = m_r_scan.get<uint32_t>(div_round_up(n_pad, 256) + 1);
+    float* frame = m_frame.get<float>((size_t)n_pixels * 4); float* fdepth = m_frame_depth.get<float>(n_pixels); float* accum = m_accum.get<float>((size_t)n_pixels * 4);
+    RenderCamera cam{};
+    cam.res[0] = w; cam.res[1] = h; cam.y0 = y0; cam.y1 = y1;
+    memcpy(cam.focal_length, focal_length, 8); memcpy(cam.screen_center, screen_center, 8); memcpy(cam.camera, camera_matrix, 48);
+    NGP_CUDA_CHECK(cudaMemsetAsync(accum, 0, (size_t)n_pixels * 16, s));
+    for (int sample = 0; sample < spp; ++sample) {
+        nerf_init_rays(s, cam, (uint32_t)sample, snap_to_pixel_centers && spp == 1, render_aabb, m_bitfield.as<uint8_t>(), m_max_cascade, cone_angle_constant, rays[0], frame, fdepth);
+        NGP_CUDA_CHECK(cudaMemsetAsync(counters, 0, 16, s));
+        uint32_t n_alive = n_pixels, i = 1, db = 0;
+        while (i < MARCH_ITER) {
+            RaysSoa& cur = rays[(db + 1) % 2]; RaysSoa& tmp = rays[db % 2]; ++db;
+            nerf_compact_rays(s, n_alive, tmp, cur, rays[2], counters, scan);
+            NGP_CUDA_CHECK(cudaMemcpyAsync(&n_alive, counters, 4, cudaMemcpyDeviceToHost, s));
+            NGP_CUDA_CHECK(cudaStreamSynchronize(s));
+            if (n_alive == 0) break;
+            const uint32_t k = std::min(std::max(2u * 1024u * 1024u / n_alive, MIN_STEPS), MAX_STEPS);   // :2574-2578
+            nerf_generate_next_inputs(s, n_alive, render_aabb, aabb, cur, input, k, m_bitfield.as<uint8_t>(), m_max_cascade, cone_angle_constant);
+            const uint32_t n_elements = (uint32_t)next_multiple((uint64_t)n_alive * k, BATCH_GRANULARITY);
+            m_nerf_net->inference(s, m_trainer->inference_params, input, n_elements, output);
+            nerf_composite(s, n_alive, i, aabb, cam.camera, cur, input, output, k, rgb_activation, density_activation, render_min_transmittance);
+            i += k;
+        }
+        uint32_t n_hit = 0;
+        NGP_CUDA_CHECK(cudaMemcpyAsync(&n_hit, counters + 1, 4, cudaMemcpyDeviceToHost, s));
+        NGP_CUDA_CHECK(cudaStreamSynchronize(s));
+        nerf_shade(s, n_hit, rays[2], linear_colors, (uint32_t)y0 * (uint32_t)w, frame, fdepth);
+        accumulate_kernel<<<div_round_up(n_pixels * 4, 256), 256, 0, s>>>(n_pixels * 4, frame, accum, 1.0f / (float)(sample + 1));
+        NGP_POST_LAUNCH();
+    }
+    NGP_CUDA_CHECK(cudaMemcpyAsync(rgba_out, accum, (size_t)n_pixels * 16, out_is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, s));
+    if (depth_out) NGP_CUDA_CHECK(cudaMemcpyAsync(depth_out, fdepth, (size_t)n_pixels * 4, out_is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, s));
+    NGP_CUDA_CHECK(cudaStreamSynchronize(s));
+}
+
+
+void Testbed::debug_buffer(const std::string& name, void** ptr, uint64_t* bytes) {
+    struct E { const char* n; DeviceBuffer* b; };
+    const E table[] = {{"coords", &m_coords}, {"numsteps", &m_numsteps}, {"ray_indices", &m_ray_indices}, {"rays", &m_rays}, {"counters", &m_counters},
+                       {"mlp_out", &m_mlp_out}, {"dloss", &m_dloss}, {"coords_compacted", &m_coords_compacted}, {"loss", &m_loss},
+                       {"grid_pos", &m_grid_pos}, {"grid_idx", &m_grid_idx}, {"grid_out", &m_grid_out}, {"density_grid_tmp", &m_density_grid_tmp},
+                       {"mean_density", &m_mean}, {"numsteps_all", &m_numsteps_all}, {"image_pos", &m_img_pos}, {"image_target", &m_img_target},
+                       {"image_out", &m_img_out}, {"image_dl", &m_img_dl}};
+    for (const E& e : table) if (name == e.n) { *ptr = e.b->ptr; *bytes = e.b->bytes; return; }
+    throw Error("debug_buffer: unknown buffer '" + name + "'");
+}
+
+}  // namespace ngp

@@ -1,0 +1,98 @@
+// Host driver of the hot path: the slice of ngp::Testbed that owns training and inference
+// (reference: include/neural-graphics-primitives/testbed.h:64-516, src/testbed.cu:3903-4151,4285-4370,
+// src/testbed_nerf.cu:3412-3609,3611-3862,3867-4152, src/testbed_image.cu:214-285,465-527).
+#pragma once
+#include "network.h"
+#include "nerf_kernels.h"
+#include "image_kernels.h"
+#include <memory>
+#include <vector>
+
+namespace ngp {
+
+enum TestbedMode : int { MODE_TB_NERF = 0, MODE_TB_SDF = 1, MODE_TB_IMAGE = 2 };
+
+struct HostImage {   // one training view handed over by the caller (host memory)
+    const void* pixels; int data_type; int res[2]; float focal_length[2]; float principal_point[2]; int lens_mode; float lens_params[4]; float xform[12];
+};
+
+struct TrainStats {
+    uint32_t training_step; float loss; uint32_t rays_per_batch, measured_batch_size, measured_batch_size_before_compaction, n_rays_total;
+    float learning_rate; float density_grid_mean;
+};
+
+class Testbed {
+public:
+    explicit Testbed(int mode);
+    ~Testbed();
+
+    // reload_network_from_json (testbed.cu:281-292) -> reset_network (testbed.cu:3903-4151)
+    void reload_network_from_json(const std::string& json);
+    // load_training_data equivalents with host buffers (NerfDataset: nerf_loader.h:110-171; load_nerf_post testbed_nerf.cu:3046-3112)
+    void set_nerf_dataset(cudaStream_t s, uint32_t n_images, const HostImage* images, int aabb_scale);
+    void set_image(cudaStream_t s, const float* rgba_host, int w, int h);
+
+    // Testbed::train (testbed.cu:4285-4370): one step.  train_begin computes gradients, train_end runs the optimizer and
+    // the NerfCounters control law; train = begin + end.  (DP: all-reduce gradient_buffer() between the two.)
+    void train(cudaStream_t s, uint32_t batch_size);
+    void train_begin(cudaStream_t s, uint32_t batch_size);
+    void train_end(cudaStream_t s, uint32_t measured_override, uint32_t measured_before_override);
+    void set_shard(uint32_t rank, uint32_t world) { m_rank = rank; m_world = world; }
+
+    // render_nerf (testbed_nerf.cu:2752-2871) into a host or device float4 buffer, rows [y0,y1), averaged over spp
+    void render(cudaStream_t s, const float* camera_matrix, const float* focal_length, const float* screen_center, int w, int h, int spp, int y0, int y1,
+                float* rgba_out, bool out_is_device, float* depth_out);
+    float compute_image_mse(cudaStream_t s, bool quantize);   // testbed_image.cu:465-527
+
+    TrainStats stats() const;
+    Trainer* trainer() { return m_trainer.get(); }
+    NerfNetwork* nerf_network() { return m_nerf_net.get(); }
+    uint64_t n_params() const { return m_trainer ? m_trainer->n_params : 0; }
+    const uint8_t* density_grid_bitfield() const { return m_bitfield.as<uint8_t>(); }
+    const float* density_grid() const { return m_density_grid.as<float>(); }
+    uint32_t max_cascade() const { return m_max_cascade; }
+    // parity hook: internal per-step buffers by name (tests compare them with the oracle)
+    void debug_buffer(const std::string& name, void** ptr, uint64_t* bytes);
+
+    // runtime knobs (pyngp def_readwrite members: python_api.cu:452-537,611-695)
+    bool random_bg_color = true, linear_colors = false, snap_to_pixel_centers = true, shall_train_encoding = true, shall_train_network = true;
+    float near_distance = 0.1f, density_grid_decay = 0.95f, render_min_transmittance = 0.01f, cone_angle_constant = 0.0f;
+    float background_color[3] = {0.f, 0.f, 0.f};
+    int loss_type = LOSS_L2, rgb_activation = ACT_LOGISTIC, density_activation = ACT_EXPONENTIAL;
+    bool image_snap_to_pixel_centers = true, image_linear_colors = false, image_stratified = true;
+    uint64_t seed = 1337;
+    Aabb aabb{{0, 0, 0}, {1, 1, 1}}, render_aabb{{0, 0, 0}, {1, 1, 1}};
+
+private:
+    void reset_network();
+    void training_prep_nerf(cudaStream_t s);                                                       // testbed_nerf.cu:4137-4152
+    void update_density_grid_nerf(cudaStream_t s, float decay, uint32_t n_uniform, uint32_t n_nonuniform);   // :3412-3536
+    void train_nerf_step(cudaStream_t s, uint32_t target_batch_size);                              // :3867-4132
+    void train_image_step(cudaStream_t s, uint32_t batch_size, bool get_loss);                     // testbed_image.cu:214-285
+
+    int m_mode;
+    Json m_config; bool m_have_config = false;
+    std::unique_ptr<NerfNetwork> m_nerf_net;
+    std::unique_ptr<EncodedMlp> m_image_net;
+    std::unique_ptr<Trainer> m_trainer;
+    uint32_t m_training_step = 0; float m_loss_scalar = 0.f; bool m_get_loss = false; uint32_t m_pending_batch = 0;
+    Pcg32 m_rng, m_density_grid_rng;
+    uint32_t m_rank = 0, m_world = 1;
+
+    // NeRF dataset + occupancy grid
+    uint32_t m_n_images = 0; int m_aabb_scale = 1; uint32_t m_max_cascade = 0;
+    std::vector<void*> m_image_buffers; DeviceBuffer m_metas;
+    DeviceBuffer m_density_grid, m_density_grid_tmp, m_bitfield, m_mean, m_partials, m_grid_pos, m_grid_idx, m_grid_out;
+    uint32_t m_density_grid_ema_step = 0; bool m_grid_allocated = false;
+    // NerfCounters (testbed.h:433-447)
+    uint32_t m_rays_per_batch = 1u << 12, m_n_rays_total = 0, m_measured = 0, m_measured_before = 0;
+    // per-step scratch
+    DeviceBuffer m_numsteps_all, m_block_steps, m_block_rays, m_ray_tmp, m_ray_indices, m_rays, m_numsteps, m_coords, m_counters, m_mlp_out, m_dloss,
+        m_coords_compacted, m_loss, m_ray_scratch, m_compacted_numsteps, m_loss_sum;
+    // image mode
+    DeviceBuffer m_image; int m_image_w = 0, m_image_h = 0; DeviceBuffer m_img_pos, m_img_target, m_img_out, m_img_dl, m_img_loss;
+    // render scratch
+    DeviceBuffer m_r_rgba[3], m_r_depth[3], m_r_payload[3], m_r_input, m_r_output, m_r_counters, m_r_scan, m_frame, m_frame_depth, m_accum;
+};
+
+}  // namespace ngp

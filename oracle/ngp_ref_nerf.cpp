@@ -126,7 +126,9 @@ static inline uint32_t mip_from_dt(float dt, V3 p, uint32_t max_cascade) {
     dt *= 2 * REF_NERF_GRIDSIZE;
     if (dt < 1.0f) return mip;
     int e; frexpf(dt, &e);
-    return (uint32_t)clampi((int)mip, e, (int)max_cascade);   // tcnn::clamp(val, lo, hi)
+    int v = (int)mip; const int lo = e, hi = (int)max_cascade;   // tcnn::clamp(val, lower, upper), testbed_nerf.cu:632
+    v = v < lo ? lo : (hi < v ? hi : v);
+    return (uint32_t)v;
 }
 static inline uint32_t cascaded_grid_idx_at(V3 p, uint32_t mip) {
     float s = scalbnf(1.0f, -(int)mip);
