@@ -169,6 +169,16 @@ int ngp_testbed_set_option(ngp_testbed_t t, const char* name, double value);
 int ngp_testbed_debug_buffer(ngp_testbed_t t, const char* name, void** dev_ptr, uint64_t* n_bytes);
 int ngp_testbed_get_option(ngp_testbed_t t, const char* name, double* value);
 
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Synthetic dataset (BASELINE.json: 100 posed 800x800 views of a procedural analytic density field; no reference
+ * counterpart — the reference loads transforms.json + images, src/nerf_loader.cu).  Data synthesis only.
+ * ------------------------------------------------------------------------------------------------------------ */
+/* camera `view` of `n_views` on an upper-hemisphere Fibonacci lattice (NGP convention mat4x3, host side) */
+int ngp_synth_camera(uint32_t view, uint32_t n_views, float radius, float* xform_out);
+/* ground-truth RGBA8 (straight-alpha sRGB) view into DEVICE memory [h][w] */
+int ngp_synth_render_view(void* stream, uint32_t view, uint32_t n_views, float radius, float focal_px, int32_t width, int32_t height, void* dev_rgba8);
+
 #ifdef __cplusplus
 }
 #endif

@@ -100,6 +100,8 @@ SYMBOLS = {
     "ngp_testbed_set_option": (i32, [vp, cp, C.c_double]),
     "ngp_testbed_get_option": (i32, [vp, cp, C.POINTER(C.c_double)]),
     "ngp_testbed_debug_buffer": (i32, [vp, cp, C.POINTER(vp), C.POINTER(u64)]),
+    "ngp_synth_camera": (i32, [u32, u32, f32, C.POINTER(f32)]),
+    "ngp_synth_render_view": (i32, [vp, u32, u32, f32, f32, C.c_int32, C.c_int32, vp]),
 }
 
 

@@ -1,0 +1,243 @@
+"""`pyngp`-shaped binding over the C ABI (mirrors src/python_api.cu:266-538 of the reference).
+
+    testbed = Testbed(TestbedMode.Nerf)
+    testbed.set_nerf_dataset(views, aabb_scale=1)       # load_training_data with in-memory views (host buffers)
+    testbed.reload_network_from_json(config)
+    while testbed.frame(): ...                          # one training step per frame, as scripts/run.py:183
+    image = testbed.render(w, h, spp, linear=True)
+
+All arithmetic runs in libngp_b200.so; torch only provides the CUDA stream and (for data-parallel training) the
+NCCL process group that all-reduces the flat fp16 gradient buffer between train_begin() and train_end().
+"""
+import ctypes as C
+import enum
+import json as _json
+
+import numpy as np
+import torch
+
+from ._lib import TrainingImage, TrainStats, check, lib
+
+
+class TestbedMode(enum.IntEnum):      # python_api.cu:271-277
+    Nerf = 0
+    Sdf = 1
+    Image = 2
+
+
+class LossType(enum.IntEnum):         # python_api.cu:311-319
+    L2 = 0
+    L1 = 1
+    Mape = 2
+    Smape = 3
+    Huber = 4
+    LogL1 = 5
+    RelativeL2 = 6
+
+
+class NerfActivation(enum.IntEnum):   # python_api.cu:321-327
+    None_ = 0
+    ReLU = 1
+    Logistic = 2
+    Exponential = 3
+
+
+class LensMode(enum.IntEnum):
+    Perspective = 0
+    OpenCV = 1
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+_BOOL_OPTS = {"random_bg_color", "linear_colors", "snap_to_pixel_centers", "shall_train_encoding", "shall_train_network",
+              "image_snap_to_pixel_centers", "image_linear_colors", "image_stratified"}
+_FLOAT_OPTS = {"near_distance", "density_grid_decay", "render_min_transmittance", "cone_angle_constant"}
+_INT_OPTS = {"loss_type", "rgb_activation", "density_activation", "seed"}
+
+
+class Testbed:
+    def __init__(self, mode=TestbedMode.Nerf):
+        object.__setattr__(self, "_h", C.c_void_p())
+        check(lib().ngp_testbed_create(int(mode), C.byref(self._h)))
+        object.__setattr__(self, "mode", TestbedMode(int(mode)))
+        object.__setattr__(self, "training_batch_size", 1 << 18)    # testbed.h:1005
+        object.__setattr__(self, "shall_train", True)
+        object.__setattr__(self, "_keep", [])
+        object.__setattr__(self, "_dist", None)
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().ngp_testbed_destroy(self._h)
+
+    # ---- runtime knobs (def_readwrite members) ----
+    def __getattr__(self, name):
+        if name in _BOOL_OPTS | _FLOAT_OPTS | _INT_OPTS:
+            v = C.c_double()
+            check(lib().ngp_testbed_get_option(self._h, name.encode(), C.byref(v)))
+            return bool(v.value) if name in _BOOL_OPTS else (float(v.value) if name in _FLOAT_OPTS else int(v.value))
+        raise AttributeError(name)
+
+    def __setattr__(self, name, value):
+        if name in _BOOL_OPTS | _FLOAT_OPTS | _INT_OPTS:
+            check(lib().ngp_testbed_set_option(self._h, name.encode(), float(value)))
+        elif name == "background_color":
+            for k, c in zip("rgb", value):
+                check(lib().ngp_testbed_set_option(self._h, f"background_{k}".encode(), float(c)))
+        else:
+            object.__setattr__(self, name, value)
+
+    # ---- data ----
+    def set_nerf_dataset(self, views, aabb_scale=1):
+        """views: list of dicts {pixels: np.uint8 [H,W,4] | np.float32 [H,W,4] (host), focal_length: (fx,fy) px,
+        xform: 12 floats (NGP mat4x3 column major), principal_point=(.5,.5), lens_mode, lens_params}."""
+        arr = (TrainingImage * len(views))()
+        for i, v in enumerate(views):
+            px = v["pixels"]
+            if isinstance(px, torch.Tensor):
+                assert not px.is_cuda, "views are host buffers (pinned torch tensors or numpy arrays)"
+                dtype_byte = px.dtype == torch.uint8
+                h, w = px.shape[:2]
+                ptr = px.data_ptr()
+            else:
+                px = np.ascontiguousarray(px)
+                dtype_byte = px.dtype == np.uint8
+                h, w = px.shape[:2]
+                ptr = px.ctypes.data
+            self._keep.append(px)
+            arr[i].pixels = ptr
+            arr[i].data_type = 0 if dtype_byte else 1
+            arr[i].res = (C.c_int32 * 2)(w, h)
+            arr[i].focal_length = (C.c_float * 2)(*v["focal_length"])
+            arr[i].principal_point = (C.c_float * 2)(*v.get("principal_point", (0.5, 0.5)))
+            arr[i].lens_mode = int(v.get("lens_mode", 0))
+            arr[i].lens_params = (C.c_float * 4)(*v.get("lens_params", (0, 0, 0, 0)))
+            arr[i].xform = (C.c_float * 12)(*[float(x) for x in np.asarray(v["xform"], np.float32).reshape(-1)])
+        check(lib().ngp_testbed_set_nerf_dataset(self._h, _stream(), len(views), arr, int(aabb_scale)))
+        self._keep.clear()
+
+    def set_image(self, rgba):
+        rgba = np.ascontiguousarray(rgba, np.float32)
+        assert rgba.ndim == 3 and rgba.shape[2] == 4
+        check(lib().ngp_testbed_set_image(self._h, _stream(), rgba.ctypes.data_as(C.c_void_p), rgba.shape[1], rgba.shape[0]))
+
+    # ---- network ----
+    def reload_network_from_json(self, config, config_base_path=""):
+        cfg = config if isinstance(config, str) else _json.dumps(config)
+        check(lib().ngp_testbed_reload_network_from_json(self._h, cfg.encode()))
+
+    def reload_network_from_file(self, path):
+        with open(path) as f:
+            self.reload_network_from_json(f.read())
+
+    def n_params(self):
+        return lib().ngp_testbed_n_params(self._h)
+
+    # ---- training ----
+    def enable_data_parallel(self, process_group=None):
+        """Shard training rays over the ranks of a torch.distributed process group; gradients are summed with one
+        all_reduce over the flat fp16 gradient buffer per step (layout nerf_network.h:430-443)."""
+        import torch.distributed as dist
+        object.__setattr__(self, "_dist", (dist, process_group))
+        check(lib().ngp_testbed_set_shard(self._h, dist.get_rank(process_group), dist.get_world_size(process_group)))
+
+    def train(self, batch_size=None):
+        n = int(batch_size or self.training_batch_size)
+        if self._dist is None:
+            check(lib().ngp_testbed_train(self._h, _stream(), n))
+            return
+        dist, pg = self._dist
+        check(lib().ngp_testbed_train_begin(self._h, _stream(), n))
+        g = self.param_buffer(3)
+        dist.all_reduce(g, group=pg)
+        # keep rays_per_batch in lock-step: the control law sees the mean sample counts
+        st_before = self._local_counters()
+        c = torch.tensor(st_before, dtype=torch.int64, device=g.device)
+        dist.all_reduce(c, group=pg)
+        w = dist.get_world_size(pg)
+        m, mb = int(c[0].item()) // w, int(c[1].item()) // w
+        check(lib().ngp_testbed_train_end(self._h, _stream(), max(m, 1), max(mb, 1)))
+
+    def _local_counters(self):
+        ptr, nbytes = self.debug_buffer("counters")
+        if self.mode != TestbedMode.Nerf or not ptr:
+            return [1, 1]
+        t = _wrap(ptr, 4, torch.int32)
+        c = t.cpu().numpy().view(np.uint32)
+        return [int(c[2]), int(c[1])]
+
+    def frame(self):
+        if self.shall_train:
+            self.train(self.training_batch_size)
+        return True
+
+    @property
+    def stats(self):
+        st = TrainStats()
+        check(lib().ngp_testbed_stats(self._h, C.byref(st)))
+        return st
+
+    @property
+    def training_step(self):
+        return self.stats.training_step
+
+    @property
+    def loss(self):
+        return self.stats.loss
+
+    # ---- buffers ----
+    def param_buffer(self, which):
+        ptr, n = C.c_void_p(), C.c_uint64()
+        check(lib().ngp_testbed_param_buffer(self._h, which, C.byref(ptr), C.byref(n)))
+        return _wrap(ptr.value, n.value, torch.float32 if which == 0 else torch.float16)
+
+    def density_grid(self, which=0):
+        ptr, n = C.c_void_p(), C.c_uint64()
+        check(lib().ngp_testbed_density_grid(self._h, which, C.byref(ptr), C.byref(n)))
+        return _wrap(ptr.value, n.value // (4 if which == 0 else 1), torch.float32 if which == 0 else torch.uint8)
+
+    def debug_buffer(self, name):
+        ptr, n = C.c_void_p(), C.c_uint64()
+        check(lib().ngp_testbed_debug_buffer(self._h, name.encode(), C.byref(ptr), C.byref(n)))
+        return ptr.value, n.value
+
+    def debug_tensor(self, name, dtype, count):
+        ptr, n = self.debug_buffer(name)
+        return _wrap(ptr, count, dtype)
+
+    # ---- inference ----
+    def render(self, width, height, spp=1, linear=True, camera_matrix=None, focal_length=None, screen_center=(0.5, 0.5), y0=0, y1=None,
+               out=None, return_depth=False):
+        """float32 [rows, W, 4] linear premultiplied RGBA of rows [y0, y1) (python_api.cu:127-205, headless)."""
+        y1 = height if y1 is None else y1
+        cam = (C.c_float * 12)(*[float(x) for x in np.asarray(camera_matrix, np.float32).reshape(-1)])
+        fl = (C.c_float * 2)(*focal_length)
+        sc = (C.c_float * 2)(*screen_center)
+        rows = y1 - y0
+        dev_out = out is not None and isinstance(out, torch.Tensor) and out.is_cuda
+        if out is None:
+            out = np.empty((rows, width, 4), np.float32)
+        depth = np.empty((rows, width), np.float32) if (return_depth and not dev_out) else None
+        optr = C.c_void_p(out.data_ptr()) if isinstance(out, torch.Tensor) else out.ctypes.data_as(C.c_void_p)
+        dptr = depth.ctypes.data_as(C.c_void_p) if depth is not None else None
+        check(lib().ngp_testbed_render(self._h, _stream(), cam, fl, sc, width, height, spp, y0, y1, optr, int(dev_out), dptr))
+        return (out, depth) if return_depth else out
+
+    def compute_image_mse(self, quantize=False):
+        v = C.c_float()
+        check(lib().ngp_testbed_compute_image_mse(self._h, _stream(), int(quantize), C.byref(v)))
+        return v.value
+
+
+class _DevPtr:
+    def __init__(self, ptr, count, dtype):
+        item = torch.empty(0, dtype=dtype).element_size()
+        typestr = {torch.float32: "<f4", torch.float16: "<f2", torch.int32: "<i4", torch.uint8: "|u1"}[dtype]
+        self.__cuda_array_interface__ = {"shape": (count,), "typestr": typestr, "data": (ptr, False), "version": 2, "strides": None}
+        self._bytes = item * count
+
+
+def _wrap(ptr, count, dtype):
+    """zero-copy torch view of library-owned device memory"""
+    return torch.as_tensor(_DevPtr(ptr, count, dtype), device="cuda")
