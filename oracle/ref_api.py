@@ -217,3 +217,77 @@ def make_image(pixels, data_type, res, focal, xform, principal=(0.5, 0.5), lens_
 
 def make_aabb(lo, hi):
     a = Aabb(); a.min = (f32 * 3)(*lo); a.max = (f32 * 3)(*hi); return a
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# NeRF path wrappers
+# ---------------------------------------------------------------------------------------------------------------
+def images_from_views(views):
+    """views as given to Testbed.set_nerf_dataset -> (ctypes Image array, keepalive list)"""
+    arr = (Image * len(views))()
+    keep = []
+    for i, v in enumerate(views):
+        px = v["pixels"]
+        px = px.numpy() if hasattr(px, "numpy") else np.ascontiguousarray(px)
+        keep.append(px)
+        h, w = px.shape[:2]
+        arr[i] = make_image(px, 0 if px.dtype == np.uint8 else 1, (w, h), v["focal_length"], v["xform"], v.get("principal_point", (0.5, 0.5)),
+                            int(v.get("lens_mode", 0)), v.get("lens_params", (0, 0, 0, 0)))
+    return arr, keep
+
+
+def mark_untrained(grid, images):
+    lib().ref_mark_untrained_density_grid(u32(grid.size), P(grid), u32(len(images)), images, i32(1))
+    return grid
+
+
+def generate_grid_samples(n, seed, skip, step, aabb, grid_in, n_cascades, thresh):
+    pos = np.zeros((n, 3), np.float32); idx = np.zeros(n, np.uint32)
+    lib().ref_generate_grid_samples_nonuniform(u32(n), u64(seed), u64(skip), u32(step), C.byref(aabb), P(grid_in), P(pos), P(idx), u32(n_cascades), f32(thresh))
+    return pos, idx
+
+
+def update_bitfield(grid, n_cascades):
+    bf = np.zeros(128 ** 3 * 8 // 8, np.uint8)
+    mean = lib().ref_update_bitfield(P(grid), u32(n_cascades), P(bf))
+    return bf, float(mean)
+
+
+def generate_training_samples(n_rays, aabb, max_samples, seed, skip, images, bitfield, max_mip, snap, cone):
+    out = SamplerOut()
+    ray_indices = np.zeros(n_rays, np.uint32); rays = np.zeros((n_rays, 6), np.float32); numsteps = np.zeros((n_rays, 2), np.uint32)
+    coords = np.zeros((max_samples, 7), np.float32)
+    out.ray_indices, out.rays, out.numsteps, out.coords = P(ray_indices).value, P(rays).value, P(numsteps).value, P(coords).value
+    lib().ref_generate_training_samples(u32(n_rays), C.byref(aabb), u32(max_samples), u32(0), u64(seed), u64(skip), u32(len(images)), images,
+                                        P(bitfield), u32(max_mip), i32(int(snap)), f32(cone), C.byref(out))
+    return dict(ray_indices=ray_indices, rays=rays, numsteps=numsteps, coords=coords, ray_counter=out.ray_counter, numsteps_counter=out.numsteps_counter)
+
+
+def compute_loss(n_rays, aabb, seed, skip, max_compacted, rays_counter, cfg, images, net_out_h, ray_indices, rays, numsteps, coords):
+    out = LossOut()
+    dloss = np.zeros((max_compacted, 4), np.float16); cc = np.zeros((max_compacted, 7), np.float32); loss = np.zeros(n_rays, np.float32)
+    ns = numsteps.copy(); rgb_ray = np.zeros((n_rays, 3), np.float32)
+    out.dloss_doutput, out.coords_compacted, out.loss, out.numsteps, out.rgb_ray = P(dloss).value, P(cc).value, P(loss).value, P(ns).value, P(rgb_ray).value
+    lib().ref_compute_loss(u32(n_rays), C.byref(aabb), u32(0), u64(seed), u64(skip), u32(max_compacted), u32(rays_counter), C.byref(cfg),
+                           u32(len(images)), images, P(net_out_h), P(ray_indices), P(rays), P(coords), C.byref(out))
+    return dict(dloss=dloss, coords_compacted=cc, loss=loss, numsteps=ns, rgb_ray=rgb_ray, compacted_counter=out.compacted_counter)
+
+
+def render_nerf(rcfg, net_cfg, params_h, bitfield):
+    W, H = rcfg.res[0], rcfg.res[1]
+    rgba = np.zeros((H, W, 4), np.float32); depth = np.zeros((H, W), np.float32)
+    lib().ref_render_nerf(C.byref(rcfg), C.byref(net_cfg), P(params_h), P(bitfield), P(rgba), P(depth))
+    return rgba, depth
+
+
+def synth_views(n_views, w, h, radius, focal, step=1.73205080757 / 1024.0):
+    """CPU-rendered views of the analytic scene (for the CPU reference arm / CPU tests)."""
+    views = []
+    l = lib()
+    for i in range(n_views):
+        px = np.zeros((h, w), np.uint32)
+        l.ref_synth_render_view(u32(i), u32(n_views), f32(radius), f32(focal), i32(w), i32(h), f32(step), P(px))
+        xf = np.zeros(12, np.float32)
+        l.ref_synth_camera(u32(i), u32(n_views), f32(radius), P(xf))
+        views.append({"pixels": px.view(np.uint8).reshape(h, w, 4), "focal_length": (focal, focal), "principal_point": (0.5, 0.5), "xform": xf})
+    return views

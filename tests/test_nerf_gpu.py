@@ -1,0 +1,189 @@
+"""GPU parity of the NeRF training step / occupancy grid / tracer through the Testbed C ABI vs the CPU oracle.
+Integer paths (grid sample cells, bitfield, ray->sample compaction, traversal with cone_angle 0) are compared bit-exact."""
+import importlib
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+SMALL_CFG = {
+    "loss": {"otype": "Huber"},
+    "optimizer": {"otype": "Ema", "decay": 0.95, "nested": {"otype": "ExponentialDecay", "decay_start": 20000, "decay_interval": 10000, "decay_base": 0.33,
+                  "nested": {"otype": "Adam", "learning_rate": 1e-2, "beta1": 0.9, "beta2": 0.99, "epsilon": 1e-15, "l2_reg": 1e-6}}},
+    "encoding": {"otype": "HashGrid", "n_levels": 16, "n_features_per_level": 2, "log2_hashmap_size": 15, "base_resolution": 16, "per_level_scale": 1.3819},
+    "network": {"otype": "FullyFusedMLP", "activation": "ReLU", "output_activation": "None", "n_neurons": 64, "n_hidden_layers": 1},
+    "rgb_network": {"otype": "FullyFusedMLP", "activation": "ReLU", "output_activation": "None", "n_neurons": 64, "n_hidden_layers": 2},
+}
+BATCH = 1 << 14
+N_VIEWS, RES = 12, 96
+
+
+@pytest.fixture(scope="module")
+def env(ngp, ref):
+    pyngp = importlib.import_module("instant-ngp_b200.pyngp")
+    scene = importlib.import_module("instant-ngp_b200.scene")
+    views = scene.make_views(N_VIEWS, RES, RES)
+    images, keep = ref.images_from_views(views)
+    return dict(pyngp=pyngp, scene=scene, views=views, images=images, keep=keep)
+
+
+def _testbed(env):
+    tb = env["pyngp"].Testbed(env["pyngp"].TestbedMode.Nerf)
+    tb.set_nerf_dataset(env["views"], aabb_scale=1)
+    tb.reload_network_from_json(SMALL_CFG)
+    return tb
+
+
+def test_synthetic_views_match_cpu_generator(env, ref):
+    scene = env["scene"]
+    cpu = ref.synth_views(2, RES, RES, scene.RADIUS, scene.focal_px(RES), step=1.73205080757 / 4096.0)
+    for i in range(2):
+        a = env["views"][i]["pixels"].numpy().astype(np.int32); b = cpu[i]["pixels"].astype(np.int32)
+        assert np.abs(a - b).max() <= 2          # expf/powf last-ulp differences only
+        np.testing.assert_allclose(env["views"][i]["xform"], cpu[i]["xform"], atol=1e-6)
+    assert (env["views"][0]["pixels"].numpy()[..., 3] > 0).mean() > 0.1
+
+
+def test_occupancy_grid_first_update(env, ref):
+    tb = _testbed(env)
+    aabb = ref.make_aabb((0, 0, 0), (1, 1, 1))
+    params0 = tb.param_buffer(1).cpu().numpy().copy()
+    tb.train(BATCH)
+    NC = 128 ** 3
+    # grid sample cells + positions of the step-0 update: bit-exact (pcg32 + LCG cell pick + morton)
+    grid0 = ref.mark_untrained(np.zeros(NC, np.float32), env["images"])
+    dg_seed = np.zeros(1, np.uint32); ref.lib().ref_pcg32_fill_uint(ref.u64(1337), ref.u64(0), ref.P(dg_seed), ref.C.c_size_t(1))
+    pos, idx = ref.generate_grid_samples(NC, int(dg_seed[0]), 0, 0, aabb, grid0, 1, -0.01)
+    gidx = tb.debug_tensor("grid_idx", torch.int32, NC).cpu().numpy().view(np.uint32)
+    gpos = tb.debug_tensor("grid_pos", torch.float32, NC * 3).cpu().numpy().reshape(NC, 3)
+    assert np.array_equal(gidx, idx)
+    assert np.array_equal(gpos, pos)
+    # densities of the first 4096 samples vs the oracle network on the initial parameters
+    rcfg = ref.nerf_cfg_from_json(SMALL_CFG)
+    dens = tb.debug_tensor("grid_out", torch.float16, NC).cpu().numpy()[:4096].astype(np.float32)
+    dref = ref.nerf_density(rcfg, params0, pos[:4096].copy()).astype(np.float32)
+    np.testing.assert_allclose(dens, dref, rtol=2e-3, atol=2e-3)
+    # bitfield + mips: bit-exact given the GPU's density grid
+    grid = tb.density_grid(0).cpu().numpy()
+    bf, mean = ref.update_bitfield(grid, 1)
+    assert np.array_equal(tb.density_grid(1).cpu().numpy(), bf)
+    gmean = tb.debug_tensor("mean_density", torch.float32, 1).cpu().numpy()[0]
+    assert abs(gmean - mean) <= 1e-6 * max(1.0, abs(mean))
+    # cells no camera sees stay -1, visible ones hold max(1*decay, density)
+    assert ((grid == -1) == (grid0 == -1)).all()
+
+
+def _step_and_capture(tb, ref, env, n_warm):
+    for _ in range(n_warm):
+        tb.train(BATCH)
+    st = tb.stats
+    rpb, mb = st.rays_per_batch, st.measured_batch_size_before_compaction
+    max_samples = BATCH * 16
+    max_inference = max_samples if mb == 0 else (min(mb, max_samples) + 255) // 256 * 256
+    step = st.training_step
+    tb.train(BATCH)
+    return rpb, max_inference, step
+
+
+@pytest.mark.parametrize("n_warm", [0, 5])
+def test_sampler_and_loss_bit_exact_compaction(env, ref, n_warm):
+    tb = _testbed(env)
+    rpb, max_inf, step = _step_and_capture(tb, ref, env, n_warm)
+    aabb = ref.make_aabb((0, 0, 0), (1, 1, 1))
+    bf = tb.density_grid(1).cpu().numpy()
+    skip = 1 + step * (1 << 32)
+    o = ref.generate_training_samples(rpb, aabb, max_inf, 1337, skip, env["images"], bf, 0, True, 0.0)
+    c = tb.debug_tensor("counters", torch.int32, 4).cpu().numpy().view(np.uint32)
+    assert c[0] == o["ray_counter"] and c[1] == o["numsteps_counter"]
+    nr = int(c[0]); ns = int(min(c[1], max_inf))
+    assert nr > 0 and ns > 0
+    assert np.array_equal(tb.debug_tensor("ray_indices", torch.int32, nr).cpu().numpy().view(np.uint32), o["ray_indices"][:nr])
+    assert np.array_equal(tb.debug_tensor("rays", torch.float32, nr * 6).cpu().numpy().reshape(nr, 6), o["rays"][:nr])
+    n_written = int(o["numsteps"][:nr, 0].sum())
+    gcoords = tb.debug_tensor("coords", torch.float32, n_written * 7).cpu().numpy().reshape(n_written, 7)
+    assert np.array_equal(gcoords, o["coords"][:n_written])          # traversal bit-exact (cone_angle 0)
+
+    # loss / compaction on the GPU's own network output
+    mlp_out = tb.debug_tensor("mlp_out", torch.float16, n_written * 4).cpu().numpy().reshape(n_written, 4)
+    mean_density = float(tb.debug_tensor("mean_density", torch.float32, 1).cpu().numpy()[0])
+    cfg = ref.LossCfg(4, 2, 3, 1, 0, 1, (ref.f32 * 3)(0, 0, 0), 128.0, 0.1, mean_density)
+    lo = ref.compute_loss(rpb, aabb, 1337, skip, BATCH, nr, cfg, env["images"], mlp_out, o["ray_indices"], o["rays"], o["numsteps"], o["coords"])
+    assert c[2] == lo["compacted_counter"]
+    gns = tb.debug_tensor("numsteps", torch.int32, nr * 2).cpu().numpy().view(np.uint32).reshape(nr, 2)
+    assert np.array_equal(gns, lo["numsteps"][:nr])
+    nc = int(min(c[2], BATCH))
+    gcc = tb.debug_tensor("coords_compacted", torch.float32, BATCH * 7).cpu().numpy().reshape(BATCH, 7)
+    assert np.array_equal(gcc[:nc], lo["coords_compacted"][:nc])
+    gdl = tb.debug_tensor("dloss", torch.float16, BATCH * 4).cpu().numpy().reshape(BATCH, 4).astype(np.float32)
+    rdl = lo["dloss"][:nc].astype(np.float32)
+    scale = np.abs(rdl).max()
+    assert np.abs(gdl[:nc] - rdl).max() <= 2e-3 * scale + 1e-7, (np.abs(gdl[:nc] - rdl).max(), scale)
+    gl = tb.debug_tensor("loss", torch.float32, rpb).cpu().numpy()
+    np.testing.assert_allclose(gl[:nr], lo["loss"][:nr], rtol=1e-3, atol=1e-9)
+    # fill_rollover: rows [nc, BATCH) are cyclic copies, gradients scaled by nc/BATCH
+    if nc < BATCH:
+        src = np.arange(nc, BATCH) % nc
+        assert np.array_equal(gcc[nc:], gcc[src])
+        np.testing.assert_allclose(gdl[nc:], gdl[src] * (nc / BATCH), rtol=2e-3, atol=1e-7)
+
+
+def test_rays_per_batch_control_law(env, ref):
+    tb = _testbed(env)
+    for _ in range(8):
+        before = tb.stats
+        tb.train(BATCH)
+        after = tb.stats
+        assert after.rays_per_batch == ref.lib().ref_next_rays_per_batch(before.rays_per_batch, BATCH, after.measured_batch_size)
+    assert after.training_step == 8
+
+
+def _psnr(tb, env, view):
+    scene = env["scene"]
+    v = env["views"][view]
+    img = tb.render(RES, RES, spp=1, camera_matrix=v["xform"], focal_length=v["focal_length"])
+    px = v["pixels"].numpy().astype(np.float32) / 255.0
+    a = px[..., 3:4]
+    lin = np.where(px[..., :3] <= 0.04045, px[..., :3] / 12.92, ((px[..., :3] + 0.055) / 1.055) ** 2.4) * a
+    mse = float(((img[..., :3] - lin) ** 2).mean())
+    return -10 * np.log10(max(mse, 1e-10)), img
+
+
+def test_training_converges_and_renders(env):
+    tb = _testbed(env)
+    tb.snap_to_pixel_centers = True
+    p0, _ = _psnr(tb, env, 0)
+    losses = []
+    for i in range(300):
+        tb.train(BATCH)
+        if i % 16 == 0:
+            losses.append(tb.loss)
+    p1, img = _psnr(tb, env, 0)
+    assert losses[-1] < 0.5 * losses[0], losses
+    assert p1 > p0 + 5 and p1 > 20, (p0, p1)
+    assert np.isfinite(img).all() and img[..., 3].max() > 0.9
+
+
+def test_render_matches_oracle_and_tiles(env, ref):
+    tb = _testbed(env)
+    for _ in range(60):
+        tb.train(BATCH)
+    v = env["views"][3]
+    W = H = 48
+    f = env["scene"].focal_px(W)
+    full = tb.render(W, H, spp=1, camera_matrix=v["xform"], focal_length=(f, f))
+    top = tb.render(W, H, spp=1, camera_matrix=v["xform"], focal_length=(f, f), y0=0, y1=20)
+    bot = tb.render(W, H, spp=1, camera_matrix=v["xform"], focal_length=(f, f), y0=20, y1=H)
+    assert np.array_equal(np.concatenate([top, bot], 0), full)        # tile-sharded render == full render
+    rc = ref.RenderCfg()
+    rc.res = (ref.C.c_int32 * 2)(W, H); rc.focal_length = (ref.f32 * 2)(f, f); rc.screen_center = (ref.f32 * 2)(0.5, 0.5)
+    rc.camera = (ref.f32 * 12)(*[float(x) for x in v["xform"]])
+    rc.render_aabb = ref.make_aabb((0, 0, 0), (1, 1, 1)); rc.train_aabb = ref.make_aabb((0, 0, 0), (1, 1, 1))
+    rc.cone_angle_constant = 0.0; rc.min_transmittance = 0.01; rc.max_mip = 0; rc.spp_index = 0; rc.snap_to_pixel_centers = 1
+    rc.rgb_activation = 2; rc.density_activation = 3; rc.linear_colors = 0; rc.y0 = 0; rc.y1 = H
+    params = tb.param_buffer(2).cpu().numpy()
+    bf = tb.density_grid(1).cpu().numpy()
+    rgba, depth = ref.render_nerf(rc, ref.nerf_cfg_from_json(SMALL_CFG), params, bf)
+    assert np.abs(full - rgba).max() <= 2e-2, np.abs(full - rgba).max()
+    assert np.abs(full - rgba).mean() <= 1e-3
