@@ -26,6 +26,10 @@ const char* ngp_last_error(void);
 int ngp_abi_version(void);
 /* number of this library's kernels launched so far on this process (bench.py's gpu_launches) */
 uint64_t ngp_kernel_launch_count(void);
+/* opt-in per-kernel CUDA-event timing on the launching stream (bench.py roofline leg); report = JSON object
+ * {"<kernel group>": {"count": launches, "ms": total}} written to buf (NUL terminated) */
+void ngp_profile_enable(int on);
+int ngp_profile_report(char* buf, uint64_t buf_size, int reset);
 
 /* activation layouts for encoder outputs / MLP inputs */
 enum { NGP_LAYOUT_ROWMAJOR = 0, /* [n][C] fp16 ("AoS", tcnn::RM with one sample per row) */

@@ -56,6 +56,8 @@ SYMBOLS = {
     "ngp_last_error": (cp, []),
     "ngp_abi_version": (i32, []),
     "ngp_kernel_launch_count": (u64, []),
+    "ngp_profile_enable": (None, [i32]),
+    "ngp_profile_report": (i32, [cp, u64, i32]),
     "ngp_encoding_create": (i32, [cp, u32, C.POINTER(vp)]),
     "ngp_encoding_destroy": (None, [vp]),
     "ngp_encoding_n_params": (u64, [vp]),

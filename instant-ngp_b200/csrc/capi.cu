@@ -2,6 +2,7 @@
 // caught, stored per thread and reported as a non-zero status + ngp_last_error().
 #include "../../include/ngp_b200.h"
 #include "testbed.h"
+#include <cstring>
 
 namespace ngp { std::atomic<uint64_t> g_launch_count{0}; }
 
@@ -36,6 +37,14 @@ extern "C" {
 const char* ngp_last_error(void) { return g_last_error.c_str(); }
 int ngp_abi_version(void) { return NGP_B200_ABI_VERSION; }
 uint64_t ngp_kernel_launch_count(void) { return g_launch_count.load(); }
+void ngp_profile_enable(int on) { profile_enable(on != 0); }
+int ngp_profile_report(char* buf, uint64_t buf_size, int reset) {
+    NGP_API_BEGIN NGP_CHECK(buf && buf_size > 2, "null argument");
+    const std::string r = profile_report_json(reset != 0);
+    NGP_CHECK(r.size() + 1 <= buf_size, "profile report buffer too small");
+    memcpy(buf, r.c_str(), r.size() + 1);
+    NGP_API_END
+}
 
 // ---- encoding ----
 int ngp_encoding_create(const char* json, uint32_t n_dims, ngp_encoding_t* out) {

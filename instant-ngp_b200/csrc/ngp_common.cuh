@@ -9,6 +9,7 @@
 #include <stdexcept>
 #include <string>
 #include <atomic>
+#include "profiler.h"
 
 #define NGP_HD __host__ __device__ __forceinline__
 #define NGP_D __device__ __forceinline__

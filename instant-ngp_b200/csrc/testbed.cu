@@ -112,6 +112,7 @@ void Testbed::set_image(cudaStream_t s, const float* rgba_host, int w, int h) {
 // update_density_grid_nerf (testbed_nerf.cu:3412-3536) + training_prep_nerf (:4137-4152)
 // ---------------------------------------------------------------------------------------------------------------
 void Testbed::update_density_grid_nerf(cudaStream_t s, float decay, uint32_t n_uniform, uint32_t n_nonuniform) {
+    NGP_PROFILE_SCOPE(s, "density_grid_update");
     const uint32_t n_cascades = m_max_cascade + 1;
     const uint32_t n_elements = NERF_GRID_N_CELLS * n_cascades;
     const uint32_t n_samples = n_uniform + n_nonuniform;
@@ -206,6 +207,7 @@ TrainStats Testbed::stats() const {
 // train_nerf_step (testbed_nerf.cu:3867-4132)
 // ---------------------------------------------------------------------------------------------------------------
 void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
+    NGP_PROFILE_SCOPE(s, "train_nerf_step");
     const uint32_t max_samples = target * 16;   // "somewhat of a worst case" (:3873)
     const uint32_t R = m_rays_per_batch, max_rays = 1u << 18;
     const uint32_t max_blocks = div_round_up(max_rays, 256);

@@ -78,7 +78,7 @@ class Encoding:
         npad = (n + 7) // 8 * 8
         y = torch.zeros(npad * self.padded_output_width(), dtype=torch.float16, device="cuda")
         check(lib().ngp_encoding_forward(self._h, _stream(), _ptr(params), _ptr(x), x.shape[1], n, _ptr(y), layout))
-        return y.view(npad, -1)[:n] if layout == LAYOUT_ROWMAJOR else y
+        return y.view(npad, self.padded_output_width())[:n] if layout == LAYOUT_ROWMAJOR else y
 
     def backward(self, x, dy, grad=None, layout=LAYOUT_ROWMAJOR):
         _dev(x, torch.float32); _dev(dy, torch.float16)
