@@ -280,11 +280,12 @@ def render_nerf(rcfg, net_cfg, params_h, bitfield):
     return rgba, depth
 
 
-def synth_views(n_views, w, h, radius, focal, step=1.73205080757 / 1024.0):
-    """CPU-rendered views of the analytic scene (for the CPU reference arm / CPU tests)."""
+def synth_views(n_views, w, h, radius, focal, step=1.73205080757 / 1024.0, count=None):
+    """CPU-rendered views of the analytic scene (for the CPU reference arm / CPU tests): the first `count` cameras
+    of an `n_views`-camera lattice."""
     views = []
     l = lib()
-    for i in range(n_views):
+    for i in range(n_views if count is None else count):
         px = np.zeros((h, w), np.uint32)
         l.ref_synth_render_view(u32(i), u32(n_views), f32(radius), f32(focal), i32(w), i32(h), f32(step), P(px))
         xf = np.zeros(12, np.float32)

@@ -38,7 +38,7 @@ def _testbed(env):
 
 def test_synthetic_views_match_cpu_generator(env, ref):
     scene = env["scene"]
-    cpu = ref.synth_views(2, RES, RES, scene.RADIUS, scene.focal_px(RES), step=1.73205080757 / 4096.0)
+    cpu = ref.synth_views(N_VIEWS, RES, RES, scene.RADIUS, scene.focal_px(RES), step=1.73205080757 / 4096.0, count=2)
     for i in range(2):
         a = env["views"][i]["pixels"].numpy().astype(np.int32); b = cpu[i]["pixels"].astype(np.int32)
         assert np.abs(a[..., 3] - b[..., 3]).max() <= 2                      # alpha: expf last-ulp differences only
