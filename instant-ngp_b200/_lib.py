@@ -88,6 +88,7 @@ SYMBOLS = {
     "ngp_testbed_destroy": (None, [vp]),
     "ngp_testbed_reload_network_from_json": (i32, [vp, cp]),
     "ngp_testbed_set_nerf_dataset": (i32, [vp, vp, u32, vp, C.c_int32]),
+    "ngp_testbed_set_training_image": (i32, [vp, vp, u32, vp]),
     "ngp_testbed_set_image": (i32, [vp, vp, vp, C.c_int32, C.c_int32]),
     "ngp_testbed_train": (i32, [vp, vp, u32]),
     "ngp_testbed_train_begin": (i32, [vp, vp, u32]),

@@ -194,6 +194,11 @@ int ngp_testbed_set_nerf_dataset(ngp_testbed_t t, void* stream, uint32_t n_image
     t->tb.set_nerf_dataset(S(stream), n_images, reinterpret_cast<const HostImage*>(images), aabb_scale);
     NGP_API_END
 }
+int ngp_testbed_set_training_image(ngp_testbed_t t, void* stream, uint32_t frame_idx, const void* pixels_host) {
+    NGP_API_BEGIN require_device(); NGP_CHECK(t, "null argument");
+    t->tb.set_training_image(S(stream), frame_idx, pixels_host);
+    NGP_API_END
+}
 int ngp_testbed_set_image(ngp_testbed_t t, void* stream, const float* rgba, int32_t w, int32_t h) {
     NGP_API_BEGIN require_device(); NGP_CHECK(t && rgba, "null argument");
     t->tb.set_image(S(stream), rgba, w, h);

@@ -266,7 +266,7 @@ __global__ void grid_init_kernel(uint64_t n, Pcg32 rng, float* __restrict__ p) {
 void grid_forward(cudaStream_t s, const GridLayout& g, const __half* table, const float* x, uint32_t x_stride, uint32_t n,
                   __half* y, int y_layout) {
     if (n == 0) return;
-    NGP_PROFILE_SCOPE(s, "grid_forward");
+    NGP_PROFILE_SCOPE(s, "grid_forward", n);
     const uint32_t threads = (uint32_t)next_multiple(n, 8) * (g.padded_width / 8);
     const uint32_t blocks = div_round_up(threads, 256);
     GRID_DISPATCH(grid_forward_kernel, g, table, x, x_stride, n, y, y_layout);
@@ -275,7 +275,7 @@ void grid_forward(cudaStream_t s, const GridLayout& g, const __half* table, cons
 void grid_backward(cudaStream_t s, const GridLayout& g, const float* x, uint32_t x_stride, uint32_t n, const __half* dy,
                    int dy_layout, __half* grad) {
     if (n == 0) return;
-    NGP_PROFILE_SCOPE(s, "grid_backward");
+    NGP_PROFILE_SCOPE(s, "grid_backward", n);
     const uint32_t threads = (uint32_t)next_multiple(n, 8) * (g.padded_width / 8);
     const uint32_t blocks = div_round_up(threads, 256);
     GRID_DISPATCH(grid_backward_kernel, g, x, x_stride, n, dy, dy_layout, grad);

@@ -561,14 +561,14 @@ static uint32_t tiles_of(uint32_t n) {
 void nerf_mlp_forward(cudaStream_t s, const NerfNetDims& d, const __half* wd, const __half* wr, const __half* enc, const float* coords,
                       uint32_t n, __half* out) {
     if (n == 0) return;
-    NGP_PROFILE_SCOPE(s, "nerf_mlp_forward");
+    NGP_PROFILE_SCOPE(s, "nerf_mlp_forward", n);
     FwdParams p{wd, wr, enc, coords, out, 4, tiles_of(n)};
     NERF_DISPATCH(launch_fwd, MODE_NERF, d, s, p);
 }
 
 void nerf_mlp_density(cudaStream_t s, const NerfNetDims& d, const __half* wd, const __half* enc, uint32_t n, __half* out) {
     if (n == 0) return;
-    NGP_PROFILE_SCOPE(s, "nerf_mlp_density");
+    NGP_PROFILE_SCOPE(s, "nerf_mlp_density", n);
     FwdParams p{wd, nullptr, enc, nullptr, out, 1, tiles_of(n)};
     NerfNetDims dd = d; dd.rgb_hidden = 1;
     NERF_DISPATCH(launch_fwd, MODE_DENSITY, dd, s, p);
@@ -577,7 +577,7 @@ void nerf_mlp_density(cudaStream_t s, const NerfNetDims& d, const __half* wd, co
 void nerf_mlp_backward(cudaStream_t s, const NerfNetDims& d, const __half* wd, const __half* wr, const __half* enc, const float* coords,
                        uint32_t n, const __half* dL_dout, __half* dL_denc, float* wgrad) {
     if (n == 0) return;
-    NGP_PROFILE_SCOPE(s, "nerf_mlp_backward");
+    NGP_PROFILE_SCOPE(s, "nerf_mlp_backward", n);
     BwdParams p{wd, wr, enc, coords, dL_dout, 4, dL_denc, wgrad, tiles_of(n)};
     NERF_DISPATCH(launch_bwd, MODE_NERF, d, s, p);
 }
@@ -585,7 +585,7 @@ void nerf_mlp_backward(cudaStream_t s, const NerfNetDims& d, const __half* wd, c
 void mlp_forward(cudaStream_t s, uint32_t in_w, uint32_t nh, const __half* w, const __half* in, uint32_t n, __half* out, uint32_t out_stride) {
     if (n == 0) return;
     NGP_CHECK(out_stride % 8 == 0 && out_stride >= 16, "mlp_forward: out_stride must be a multiple of 8 and >= 16");
-    NGP_PROFILE_SCOPE(s, "mlp_forward");
+    NGP_PROFILE_SCOPE(s, "mlp_forward", n);
     FwdParams p{w, nullptr, in, nullptr, out, out_stride, tiles_of(n)};
     PLAIN_DISPATCH(launch_fwd, in_w, nh, s, p);
 }
@@ -594,7 +594,7 @@ void mlp_backward(cudaStream_t s, uint32_t in_w, uint32_t nh, const __half* w, c
                   uint32_t dout_stride, __half* dL_din, float* wgrad) {
     if (n == 0) return;
     NGP_CHECK(dout_stride % 8 == 0 && dout_stride >= 16, "mlp_backward: dout_stride must be a multiple of 8 and >= 16");
-    NGP_PROFILE_SCOPE(s, "mlp_backward");
+    NGP_PROFILE_SCOPE(s, "mlp_backward", n);
     BwdParams p{w, nullptr, in, nullptr, dL_dout, dout_stride, dL_din, wgrad, tiles_of(n)};
     PLAIN_DISPATCH(launch_bwd, in_w, nh, s, p);
 }

@@ -314,7 +314,7 @@ void nerf_generate_training_samples(cudaStream_t s, uint32_t n_rays, Aabb aabb, 
                                     uint32_t n_images, const ImageMeta* metas, const uint8_t* bitfield, uint32_t max_mip, bool snap,
                                     float cone_angle_constant, uint32_t ray_offset, uint32_t n_rays_global, const SamplerBuffers& b) {
     (void)n_rays_total;
-    NGP_PROFILE_SCOPE(s, "sampler");
+    NGP_PROFILE_SCOPE(s, "sampler", n_rays);
     const uint32_t blocks = div_round_up(n_rays, SCAN_BLOCK);
     sampler_count_kernel<<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, rng, n_images, metas, bitfield, max_mip, snap, cone_angle_constant, ray_offset, n_rays_global, b);
     NGP_POST_LAUNCH();
@@ -471,7 +471,7 @@ void nerf_compute_loss(cudaStream_t s, uint32_t n_rays, Aabb aabb, uint32_t n_ra
                        uint32_t n_images, const ImageMeta* metas, const float* mean_density_dev, uint32_t ray_offset, uint32_t n_rays_global,
                        const SamplerBuffers& sb, const LossBuffers& lb) {
     (void)n_rays_total;
-    NGP_PROFILE_SCOPE(s, "loss");
+    NGP_PROFILE_SCOPE(s, "loss", n_rays);
     const uint32_t blocks = div_round_up(n_rays, SCAN_BLOCK);
     loss_forward_kernel<<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, rng, cfg, n_images, metas, ray_offset, n_rays_global, sb, lb);
     NGP_POST_LAUNCH();
@@ -498,7 +498,7 @@ __global__ void fill_rollover_kernel(uint32_t n_target, const uint32_t* __restri
     for (int k = 0; k < 7; ++k) coords[(size_t)i * 7 + k] = coords[(size_t)src * 7 + k];
 }
 void nerf_fill_rollover(cudaStream_t s, uint32_t n_target, const uint32_t* n_input_dev, __half* dloss, float* coords) {
-    NGP_PROFILE_SCOPE(s, "fill_rollover");
+    NGP_PROFILE_SCOPE(s, "fill_rollover", n_target);
     fill_rollover_kernel<<<div_round_up(n_target, 256), 256, 0, s>>>(n_target, n_input_dev, dloss, coords);
     NGP_POST_LAUNCH();
 }

@@ -43,7 +43,7 @@ __global__ void __launch_bounds__(256) adam_kernel(const AdamHyper h, uint64_t n
 void adam_step(cudaStream_t s, const AdamHyper& h, uint64_t n, float* master, __half* params, const __half* grads, float* m, float* v,
                uint32_t* steps, float* ema_f32, __half* ema_half) {
     if (n == 0) return;
-    NGP_PROFILE_SCOPE(s, "adam");
+    NGP_PROFILE_SCOPE(s, "adam", n);
     float od = 0.f, nd = 1.f;
     if (ema_f32) { od = 1.0f - powf(h.ema_decay, (float)(h.ema_step - 1)); nd = 1.0f - powf(h.ema_decay, (float)h.ema_step); }
     adam_kernel<<<(uint32_t)((n + 255) / 256), 256, 0, s>>>(h, n, master, params, grads, m, v, steps, ema_f32, ema_half, od, nd);

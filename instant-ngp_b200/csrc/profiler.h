@@ -2,14 +2,15 @@
 // NGP_PROFILE_SCOPE costs one relaxed atomic load when off.
 #pragma once
 #include <cuda_runtime.h>
+#include <cstdint>
 #include <string>
 namespace ngp {
 struct ProfileScope {
-    ProfileScope(cudaStream_t s, const char* name);
+    ProfileScope(cudaStream_t s, const char* name, uint64_t units = 0);   // units: work items of this launch (points, samples, params)
     ~ProfileScope();
     cudaStream_t s; int slot;
 };
 void profile_enable(bool on);
-std::string profile_report_json(bool reset);   // {"name": {"count": n, "ms": total}, ...}; synchronises the device
+std::string profile_report_json(bool reset);   // {"name": {"count": n, "ms": total, "units": total}, ...}; synchronises the device
 }
-#define NGP_PROFILE_SCOPE(stream, name) ngp::ProfileScope _ngp_prof_scope((stream), (name))
+#define NGP_PROFILE_SCOPE(stream, ...) ngp::ProfileScope _ngp_prof_scope((stream), __VA_ARGS__)

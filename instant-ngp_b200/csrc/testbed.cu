@@ -60,7 +60,7 @@ void Testbed::set_nerf_dataset(cudaStream_t s, uint32_t n_images, const HostImag
     NGP_CHECK(aabb_scale >= 1 && (aabb_scale & (aabb_scale - 1)) == 0, "NeRF dataset's `aabb_scale` must be a power of two");
     NGP_CHECK(aabb_scale <= (1 << (NERF_CASCADES - 1)), "NeRF dataset must have `aabb_scale <= 128`");
     for (void* p : m_image_buffers) cudaFree(p);
-    m_image_buffers.clear();
+    m_image_buffers.clear(); m_image_bytes.clear();
     std::vector<ImageMeta> metas(n_images);
     for (uint32_t i = 0; i < n_images; ++i) {
         const HostImage& h = images[i];
@@ -69,7 +69,7 @@ void Testbed::set_nerf_dataset(cudaStream_t s, uint32_t n_images, const HostImag
         const size_t bytes = (size_t)h.res[0] * h.res[1] * (h.data_type == IMG_BYTE ? 4 : 16);
         void* d = nullptr;
         NGP_CUDA_CHECK(cudaMalloc(&d, bytes));
-        m_image_buffers.push_back(d);
+        m_image_buffers.push_back(d); m_image_bytes.push_back(bytes);
         NGP_CUDA_CHECK(cudaMemcpyAsync(d, h.pixels, bytes, cudaMemcpyHostToDevice, s));
         ImageMeta& m = metas[i];
         m.pixels = d; m.data_type = h.data_type; m.lens_mode = h.lens_mode;
@@ -98,6 +98,13 @@ void Testbed::set_nerf_dataset(cudaStream_t s, uint32_t n_images, const HostImag
     m_grid_allocated = true;
     m_training_step = 0; m_density_grid_ema_step = 0;
     NGP_CUDA_CHECK(cudaStreamSynchronize(s));
+}
+
+void Testbed::set_training_image(cudaStream_t s, uint32_t frame_idx, const void* pixels_host) {
+    NGP_CHECK(m_mode == MODE_TB_NERF, "set_training_image: testbed is not in Nerf mode");
+    NGP_CHECK(frame_idx < m_n_images, "Invalid frame index");   // python_api.cu:50-52
+    NGP_CHECK(pixels_host, "set_training_image: null pixels");
+    NGP_CUDA_CHECK(cudaMemcpyAsync(m_image_buffers[frame_idx], pixels_host, m_image_bytes[frame_idx], cudaMemcpyHostToDevice, s));
 }
 
 void Testbed::set_image(cudaStream_t s, const float* rgba_host, int w, int h) {

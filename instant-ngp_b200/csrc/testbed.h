@@ -31,6 +31,9 @@ public:
     // load_training_data equivalents with host buffers (NerfDataset: nerf_loader.h:110-171; load_nerf_post testbed_nerf.cu:3046-3112)
     void set_nerf_dataset(cudaStream_t s, uint32_t n_images, const HostImage* images, int aabb_scale);
     void set_image(cudaStream_t s, const float* rgba_host, int w, int h);
+    // nerf.training.set_image (python_api.cu:49-67): replace the pixels of one training view (same resolution / type),
+    // host -> device on `s`; asynchronous with respect to the host when the source is pinned
+    void set_training_image(cudaStream_t s, uint32_t frame_idx, const void* pixels_host);
 
     // Testbed::train (testbed.cu:4285-4370): one step.  train_begin computes gradients, train_end runs the optimizer and
     // the NerfCounters control law; train = begin + end.  (DP: all-reduce gradient_buffer() between the two.)
@@ -81,7 +84,7 @@ private:
 
     // NeRF dataset + occupancy grid
     uint32_t m_n_images = 0; int m_aabb_scale = 1; uint32_t m_max_cascade = 0;
-    std::vector<void*> m_image_buffers; DeviceBuffer m_metas;
+    std::vector<void*> m_image_buffers; std::vector<size_t> m_image_bytes; DeviceBuffer m_metas;
     DeviceBuffer m_density_grid, m_density_grid_tmp, m_bitfield, m_mean, m_partials, m_grid_pos, m_grid_idx, m_grid_out;
     uint32_t m_density_grid_ema_step = 0; bool m_grid_allocated = false;
     // NerfCounters (testbed.h:433-447)

@@ -117,6 +117,15 @@ class Testbed:
         check(lib().ngp_testbed_set_nerf_dataset(self._h, _stream(), len(views), arr, int(aabb_scale)))
         self._keep.clear()
 
+    def set_training_image(self, frame_idx, pixels):
+        """nerf.training.set_image(frame_idx, img) (python_api.cu:49-67): host pixels -> the device copy of one view."""
+        if isinstance(pixels, torch.Tensor):
+            assert not pixels.is_cuda and pixels.is_contiguous()
+            ptr = pixels.data_ptr()
+        else:
+            pixels = np.ascontiguousarray(pixels); ptr = pixels.ctypes.data
+        check(lib().ngp_testbed_set_training_image(self._h, _stream(), int(frame_idx), C.c_void_p(ptr)))
+
     def set_image(self, rgba):
         rgba = np.ascontiguousarray(rgba, np.float32)
         assert rgba.ndim == 3 and rgba.shape[2] == 4
