@@ -35,7 +35,7 @@ METRIC = "nerf_train_samples_per_s"
 UNIT = "samples/s"
 N_VIEWS, RES = 100, 800
 BATCH = 1 << 18
-PRETRAIN = 256          # untimed steps before warm-up: past the "every step refreshes all 128^3 cells" phase (testbed_nerf.cu:4143)
+PRETRAIN = 1024         # untimed steps before warm-up: the occupancy grid has sparsified and rays_per_batch has settled (tools/phase_profile.py)
 
 
 def network_config(log2_hashmap_size=19):
@@ -250,8 +250,13 @@ def run_own(args):
             c = torch.tensor([n, nb], dtype=torch.float64, device="cuda"); dist.all_reduce(c); n, nb = int(c[0].item()), int(c[1].item())
         return ms, n, nb, launches
 
+    ncu = os.environ.get("NGP_NCU") == "1"      # under `ncu --profile-from-start off`: capture only the timed steps
+    if ncu:
+        torch.cuda.profiler.start()
     with ClockSampler(local) as clk:
         ms, n_samples, n_before, launches = timed(args.steps, upload=False)
+    if ncu:
+        torch.cuda.profiler.stop()
     clocks = clk.summary()
     ms_e2e, n_e2e, _, _ = timed(args.steps, upload=True)
     view_bytes = int(views[0]["pixels"].numel())

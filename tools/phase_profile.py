@@ -1,0 +1,31 @@
+"""Per-kernel step profile at several points of a NeRF training run (tools, not product): how the step mix moves as the
+occupancy grid sparsifies and rays_per_batch adapts."""
+import ctypes as C, importlib, json, sys, os, time
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np, torch
+import bench
+pyngp = importlib.import_module("instant-ngp_b200.pyngp"); scene = importlib.import_module("instant-ngp_b200.scene")
+lib = importlib.import_module("instant-ngp_b200._lib").lib()
+nv, res = int(sys.argv[1]) if len(sys.argv) > 1 else 100, int(sys.argv[2]) if len(sys.argv) > 2 else 800
+views = scene.make_views(nv, res, res)
+tb = pyngp.Testbed(pyngp.TestbedMode.Nerf); tb.set_nerf_dataset(views, aabb_scale=1); tb.reload_network_from_json(bench.network_config(19))
+buf = C.create_string_buffer(1 << 16)
+def psnr(view):
+    v = views[view]; W = 200; f = scene.focal_px(W)
+    img = tb.render(W, W, spp=1, camera_matrix=v["xform"], focal_length=(f, f))
+    px = v["pixels"].numpy()[::res // W, ::res // W].astype(np.float32) / 255.0
+    a = px[..., 3:4]; lin = np.where(px[..., :3] <= 0.04045, px[..., :3] / 12.92, ((px[..., :3] + 0.055) / 1.055) ** 2.4) * a
+    return -10 * np.log10(max(float(((img[..., :3] - lin) ** 2).mean()), 1e-10))
+marks = [int(x) for x in (sys.argv[3].split(",") if len(sys.argv) > 3 else "64,256,512,1000,2000,4000".split(","))]
+step = 0
+for m in marks:
+    while step < m: tb.train(1 << 18); step += 1
+    lib.ngp_profile_enable(1); lib.ngp_profile_report(buf, len(buf), 1)
+    torch.cuda.synchronize(); t0 = time.perf_counter()
+    for _ in range(32): tb.train(1 << 18); step += 1
+    torch.cuda.synchronize(); dt = (time.perf_counter() - t0) / 32 * 1e3
+    lib.ngp_profile_report(buf, len(buf), 1); lib.ngp_profile_enable(0)
+    prof = json.loads(buf.value.decode()); st = tb.stats
+    print(json.dumps({"step": step, "ms_per_step_wall": round(dt, 3), "rays_per_batch": st.rays_per_batch, "measured": st.measured_batch_size,
+                      "before": st.measured_batch_size_before_compaction, "loss": st.loss, "psnr_view0": round(psnr(0), 2),
+                      "kernels_ms_per_step": {k: round(v["ms"] / 32, 4) for k, v in prof.items()}}), flush=True)
