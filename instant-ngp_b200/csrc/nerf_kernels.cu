@@ -310,17 +310,148 @@ __global__ void __launch_bounds__(SCAN_BLOCK) sampler_write_kernel(uint32_t n_ra
     march_training_ray<true>(o, normalize3(du), rt[6], rt[7], aabb, bitfield, max_mip, numsteps, b.coords + (size_t)base * 7);
 }
 
+// ---- warp-cooperative marcher: G lanes per ray ------------------------------------------------------------------
+// The reference walks a ray serially (one thread per ray); t_{k+1} depends on t_k through float rounding, so the chain
+// itself cannot be re-associated without changing traversal decisions.  What CAN be taken off the serial path are the
+// occupancy look-ups: the successor of a candidate is step(t) if its cell is occupied and skip(t) if it is not, and both
+// are pure functions of t.  The G lanes of a group therefore run the chain in lock-step under the assumption that the
+// current run (occupied / empty) continues, lane k keeping candidate k, then test all G cells with one ballot.  The
+// candidates up to the first misprediction are exactly the serial walk's; the group restarts from there in the other
+// mode.  Every float operation is the serial one, so positions, sample counts and coordinates are bit-identical.
+template <uint32_t G, bool WRITE>
+NGP_D uint32_t march_training_ray_group(V3 o, V3 d, float startt, float cone, const Aabb& aabb, const uint8_t* __restrict__ bitfield, uint32_t max_mip,
+                                        uint32_t limit, float* __restrict__ coords, uint32_t lane, uint32_t gshift, uint32_t gmask) {
+    constexpr uint32_t FULL = G == 32 ? 0xffffffffu : ((1u << G) - 1u);
+    if (limit == 0) return 0;
+    const V3 idir = v3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+    const V3 wd = warp_direction(d);
+    uint32_t j = 0; float t_base = startt; bool step_mode = false;
+    while (true) {
+        float t = t_base, my_t = 0.f, my_dt = 0.f; V3 my_pos = v3(0.f, 0.f, 0.f); uint32_t my_mip = 0, n_valid = G;
+#pragma unroll 1
+        for (uint32_t it = 0; it < G; ++it) {
+            const V3 pos = ray_at(o, d, t);
+            if (!aabb_contains(aabb, pos)) { n_valid = it; break; }
+            const float dt = calc_dt(t, cone);
+            const uint32_t mip = mip_from_dt(dt, pos, max_mip);
+            if (it == lane) { my_t = t; my_dt = dt; my_pos = pos; my_mip = mip; }
+            t = step_mode ? t + dt : advance_to_next_voxel(t, cone, pos, d, idir, mip);
+        }
+        const bool occ = lane < n_valid && density_grid_occupied_at(my_pos, bitfield, my_mip);
+        const uint32_t occ_mask = (__ballot_sync(gmask, occ) >> gshift) & FULL;
+        if (step_mode) {
+            const uint32_t bad = ~occ_mask & FULL;
+            const uint32_t f = bad ? (uint32_t)__ffs((int)bad) - 1u : G;     // first candidate that is not an occupied sample
+            const uint32_t n_emit = min(f, limit - j);
+            if (WRITE && lane < n_emit) {
+                float* c = coords + (size_t)(j + lane) * 7;
+                const V3 wp = warp_position(my_pos, aabb);
+                c[0] = wp.x; c[1] = wp.y; c[2] = wp.z; c[3] = warp_dt(my_dt); c[4] = wd.x; c[5] = wd.y; c[6] = wd.z;
+            }
+            j += n_emit;
+            if (j >= limit) break;
+            if (f == G) { t_base = t; continue; }
+            if (f >= n_valid) break;                                         // candidate f left the aabb: end of the walk
+            const float my_skip = advance_to_next_voxel(my_t, cone, my_pos, d, idir, my_mip);
+            t_base = __shfl_sync(gmask, my_skip, gshift + f);
+            step_mode = false;
+        } else {
+            if (occ_mask) { t_base = __shfl_sync(gmask, my_t, gshift + (uint32_t)__ffs((int)occ_mask) - 1u); step_mode = true; continue; }
+            if (n_valid < G) break;
+            t_base = t;
+        }
+    }
+    return j;
+}
+
+template <uint32_t G>
+__global__ void __launch_bounds__(SCAN_BLOCK) sampler_count_group_kernel(uint32_t n_rays, Aabb aabb, Pcg32 rng, uint32_t n_images, const ImageMeta* __restrict__ metas,
+                                                                         const uint8_t* __restrict__ bitfield, uint32_t max_mip, bool snap, float cone_angle_constant,
+                                                                         uint32_t ray_offset, uint32_t n_rays_global, SamplerBuffers b) {
+    constexpr uint32_t RPB = SCAN_BLOCK / G;
+    const uint32_t lane = threadIdx.x % G, gshift = (threadIdx.x & 31u) / G * G;
+    const uint32_t gmask = G == 32 ? 0xffffffffu : (((1u << G) - 1u) << gshift);
+    const uint32_t i = blockIdx.x * RPB + threadIdx.x / G;
+    uint32_t numsteps = 0;
+    if (i < n_rays) {   // group-uniform: every lane of the group builds the same ray
+        const uint32_t ig = ray_offset + i;
+        const uint32_t img = image_idx(ig, n_rays_global, n_images);
+        const ImageMeta& m = metas[img];
+        rng.advance((int64_t)((uint64_t)ig * N_MAX_RANDOM_SAMPLES_PER_RAY));
+        float uv[2]; random_image_pos_training(rng, m.res, snap, uv);
+        float texel[4]; read_rgba(m, uv[0], uv[1], texel);
+        if (texel[0] >= 0.0f) {
+            (void)rng.next_float();
+            V3 o, du; uv_to_ray(m.xform, m.res, m.focal_length, m.principal_point, m.lens_mode, m.lens_params, uv[0], uv[1], o, du);
+            if (du.x == 0.f && du.y == 0.f && du.z == 0.f) { o = v3(m.xform[9], m.xform[10], m.xform[11]); du = v3(m.xform[6], m.xform[7], m.xform[8]); }
+            const V3 d = normalize3(du);
+            float tmin, tmax; aabb_ray_intersect(aabb, o, d, tmin, tmax);
+            const float cone = cone_angle_constant;
+            tmin = fmaxf(tmin, 0.0f);
+            const float startt = advance_n_steps(tmin, cone, rng.next_float());
+            numsteps = march_training_ray_group<G, false>(o, d, startt, cone, aabb, bitfield, max_mip, NERF_STEPS, nullptr, lane, gshift, gmask);
+            if (lane == 0) {
+                float* rt = b.ray_tmp + (size_t)i * 8;
+                rt[0] = o.x; rt[1] = o.y; rt[2] = o.z; rt[3] = du.x; rt[4] = du.y; rt[5] = du.z; rt[6] = startt; rt[7] = cone;
+            }
+        }
+        if (lane == 0) b.numsteps_all[i] = numsteps;
+    }
+    const uint32_t v = lane == 0 ? numsteps : 0u;
+    uint32_t total_steps, total_rays;
+    block_exclusive_scan(v, total_steps);
+    block_exclusive_scan(v > 0 ? 1u : 0u, total_rays);
+    if (threadIdx.x == 0) { b.block_steps[blockIdx.x] = total_steps; b.block_rays[blockIdx.x] = total_rays; }
+}
+
+template <uint32_t G>
+__global__ void __launch_bounds__(SCAN_BLOCK) sampler_write_group_kernel(uint32_t n_rays, Aabb aabb, uint32_t max_samples, const uint8_t* __restrict__ bitfield,
+                                                                         uint32_t max_mip, SamplerBuffers b) {
+    constexpr uint32_t RPB = SCAN_BLOCK / G;
+    const uint32_t lane = threadIdx.x % G, gshift = (threadIdx.x & 31u) / G * G;
+    const uint32_t gmask = G == 32 ? 0xffffffffu : (((1u << G) - 1u) << gshift);
+    const uint32_t i = blockIdx.x * RPB + threadIdx.x / G;
+    const uint32_t numsteps = i < n_rays ? b.numsteps_all[i] : 0;
+    const uint32_t v = lane == 0 ? numsteps : 0u;
+    uint32_t tot;
+    const uint32_t base = __shfl_sync(gmask, b.block_steps[blockIdx.x] + block_exclusive_scan(v, tot), gshift);
+    const uint32_t ray_idx = __shfl_sync(gmask, b.block_rays[blockIdx.x] + block_exclusive_scan(v > 0 ? 1u : 0u, tot), gshift);
+    const bool keep = numsteps > 0 && base + numsteps <= max_samples;
+    uint32_t kept_total;
+    block_exclusive_scan(keep && lane == 0 ? 1u : 0u, kept_total);
+    if (threadIdx.x == 0 && kept_total) atomicAdd(&b.counters[0], kept_total);
+    if (!keep) return;
+    const float* rt = b.ray_tmp + (size_t)i * 8;
+    const V3 o = ld3(rt), du = ld3(rt + 3);
+    if (lane == 0) {
+        b.ray_indices[ray_idx] = i;
+        float* r = b.rays + (size_t)ray_idx * 6;
+        r[0] = o.x; r[1] = o.y; r[2] = o.z; r[3] = du.x; r[4] = du.y; r[5] = du.z;
+        b.numsteps[ray_idx * 2 + 0] = numsteps; b.numsteps[ray_idx * 2 + 1] = base;
+    }
+    march_training_ray_group<G, true>(o, normalize3(du), rt[6], rt[7], aabb, bitfield, max_mip, numsteps, b.coords + (size_t)base * 7, lane, gshift, gmask);
+}
+
+// lanes per ray: few long rays -> a whole warp per ray; the usual tens of thousands of rays -> 8 lanes; beyond that the
+// lock-step chain's redundancy costs more issue slots than the look-up latency it hides -> one thread per ray
+uint32_t nerf_sampler_lanes_per_ray(uint32_t n_rays) { return n_rays <= 2048 ? 32u : (n_rays <= 65536 ? 8u : 1u); }
+
 void nerf_generate_training_samples(cudaStream_t s, uint32_t n_rays, Aabb aabb, uint32_t max_samples, uint32_t n_rays_total, Pcg32 rng,
                                     uint32_t n_images, const ImageMeta* metas, const uint8_t* bitfield, uint32_t max_mip, bool snap,
                                     float cone_angle_constant, uint32_t ray_offset, uint32_t n_rays_global, const SamplerBuffers& b) {
     (void)n_rays_total;
     NGP_PROFILE_SCOPE(s, "sampler", n_rays);
-    const uint32_t blocks = div_round_up(n_rays, SCAN_BLOCK);
-    sampler_count_kernel<<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, rng, n_images, metas, bitfield, max_mip, snap, cone_angle_constant, ray_offset, n_rays_global, b);
+    const uint32_t G = b.lanes_per_ray ? b.lanes_per_ray : nerf_sampler_lanes_per_ray(n_rays);
+    const uint32_t blocks = div_round_up(n_rays, SCAN_BLOCK / G);
+    if (G == 32) sampler_count_group_kernel<32><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, rng, n_images, metas, bitfield, max_mip, snap, cone_angle_constant, ray_offset, n_rays_global, b);
+    else if (G == 8) sampler_count_group_kernel<8><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, rng, n_images, metas, bitfield, max_mip, snap, cone_angle_constant, ray_offset, n_rays_global, b);
+    else sampler_count_kernel<<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, rng, n_images, metas, bitfield, max_mip, snap, cone_angle_constant, ray_offset, n_rays_global, b);
     NGP_POST_LAUNCH();
     scan_block_totals_kernel<<<1, 1024, 0, s>>>(blocks, b.block_steps, b.block_rays, &b.counters[1], nullptr, false);
     NGP_POST_LAUNCH();
-    sampler_write_kernel<<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, max_samples, bitfield, max_mip, b);
+    if (G == 32) sampler_write_group_kernel<32><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, max_samples, bitfield, max_mip, b);
+    else if (G == 8) sampler_write_group_kernel<8><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, max_samples, bitfield, max_mip, b);
+    else sampler_write_kernel<<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, max_samples, bitfield, max_mip, b);
     NGP_POST_LAUNCH();
 }
 
@@ -467,17 +598,168 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_backward_kernel(uint32_t n_ra
     }
 }
 
+// ---- G lanes per ray: samples are loaded and activated in parallel (coalesced 8 B / 28 B per lane), the transmittance and
+// colour recurrences are then replayed in sample order with group shuffles, one multiply-add chain per sample — the same
+// float operations in the same order as the serial loop, so the compaction cut-off (T < 1e-4) is bit-identical.
+template <uint32_t G>
+__global__ void __launch_bounds__(SCAN_BLOCK) loss_forward_group_kernel(uint32_t n_rays, Pcg32 rng, LossConfig cfg, uint32_t n_images, const ImageMeta* __restrict__ metas,
+                                                                        uint32_t ray_offset, uint32_t n_rays_global, SamplerBuffers sb, LossBuffers lb) {
+    constexpr uint32_t RPB = SCAN_BLOCK / G;
+    const uint32_t lane = threadIdx.x % G, gshift = (threadIdx.x & 31u) / G * G;
+    const uint32_t gmask = G == 32 ? 0xffffffffu : (((1u << G) - 1u) << gshift);
+    const uint32_t i = blockIdx.x * RPB + threadIdx.x / G;
+    uint32_t cn = 0;
+    if (i < sb.counters[0]) {
+        const uint32_t numsteps = sb.numsteps[i * 2 + 0], base = sb.numsteps[i * 2 + 1];
+        const float* cin = sb.coords + (size_t)base * 7;
+        const __half* no = lb.network_output + (size_t)base * 4;
+        float T = 1.f; const float epsilon = 1e-4f;
+        V3 rgb_ray = v3(0, 0, 0);
+        bool stop = false;
+        for (uint32_t c0 = 0; c0 < numsteps && !stop; c0 += G) {
+            const uint32_t idx = c0 + lane;
+            float alpha = 0.f; V3 rgb = v3(0, 0, 0);
+            if (idx < numsteps) {
+                float o[4]; load_out4(no + (size_t)idx * 4, o);
+                rgb = v3(network_to_rgb(o[0], cfg.rgb_activation), network_to_rgb(o[1], cfg.rgb_activation), network_to_rgb(o[2], cfg.rgb_activation));
+                const float dt = unwarp_dt(__ldg(cin + (size_t)idx * 7 + 3));
+                const float density = network_to_density(o[3], cfg.density_activation);
+                alpha = 1.f - expf(-density * dt);
+            }
+            const uint32_t n = min(G, numsteps - c0);
+            for (uint32_t k = 0; k < n; ++k) {
+                if (T < epsilon) { stop = true; break; }
+                const float a = __shfl_sync(gmask, alpha, gshift + k);
+                const V3 r = v3(__shfl_sync(gmask, rgb.x, gshift + k), __shfl_sync(gmask, rgb.y, gshift + k), __shfl_sync(gmask, rgb.z, gshift + k));
+                const float weight = a * T;
+                rgb_ray = rgb_ray + weight * r;
+                T *= (1.f - a);
+                ++cn;
+            }
+        }
+        if (lane == 0) {
+            const uint32_t ig = ray_offset + sb.ray_indices[i];
+            rng.advance((int64_t)((uint64_t)ig * N_MAX_RANDOM_SAMPLES_PER_RAY));
+            const ImageMeta& m = metas[image_idx(ig, n_rays_global, n_images)];
+            float uv[2]; random_image_pos_training(rng, m.res, cfg.snap_to_pixel_centers, uv);
+            rng.advance(1);
+            V3 bg = ld3(cfg.background_color);
+            if (cfg.random_bg_color) { const float a = rng.next_float(), b = rng.next_float(), c = rng.next_float(); bg = v3(a, b, c); }
+            bg = v3(srgb_to_linear(bg.x), srgb_to_linear(bg.y), srgb_to_linear(bg.z));
+            float tex[4]; read_rgba(m, uv[0], uv[1], tex);
+            const V3 trgb = v3(tex[0], tex[1], tex[2]); const float ta = tex[3];
+            V3 target;
+            if (cfg.linear_colors) {
+                target = trgb + (1.0f - ta) * bg;
+            } else {
+                bg = v3(linear_to_srgb(bg.x), linear_to_srgb(bg.y), linear_to_srgb(bg.z));
+                if (ta > 0) {
+                    const V3 q = v3(linear_to_srgb(trgb.x / ta), linear_to_srgb(trgb.y / ta), linear_to_srgb(trgb.z / ta));
+                    target = q * ta + (1.0f - ta) * bg;
+                } else target = bg;
+            }
+            if (cn == numsteps) rgb_ray = rgb_ray + T * bg;
+            float* rs = lb.ray_scratch + (size_t)i * 8;
+            rs[0] = rgb_ray.x; rs[1] = rgb_ray.y; rs[2] = rgb_ray.z; rs[3] = target.x; rs[4] = target.y; rs[5] = target.z;
+            lb.compacted_numsteps[i] = cn;
+        }
+    }
+    uint32_t total;
+    block_exclusive_scan(lane == 0 ? cn : 0u, total);
+    if (threadIdx.x == 0) sb.block_steps[blockIdx.x] = total;
+}
+
+template <uint32_t G>
+__global__ void __launch_bounds__(SCAN_BLOCK) loss_backward_group_kernel(uint32_t n_rays, Aabb aabb, uint32_t max_compacted, LossConfig cfg,
+                                                                         const float* __restrict__ mean_density, uint32_t n_rays_global, SamplerBuffers sb, LossBuffers lb) {
+    constexpr uint32_t RPB = SCAN_BLOCK / G;
+    const uint32_t lane = threadIdx.x % G, gshift = (threadIdx.x & 31u) / G * G;
+    const uint32_t gmask = G == 32 ? 0xffffffffu : (((1u << G) - 1u) << gshift);
+    const uint32_t i = blockIdx.x * RPB + threadIdx.x / G;
+    const bool active = i < sb.counters[0];
+    uint32_t cn = active ? lb.compacted_numsteps[i] : 0;
+    uint32_t total;
+    const uint32_t cbase = __shfl_sync(gmask, sb.block_steps[blockIdx.x] + block_exclusive_scan(lane == 0 ? cn : 0u, total), gshift);
+    if (!active) return;
+    const uint32_t base = sb.numsteps[i * 2 + 1];
+    __syncwarp(gmask);   // every lane has read (numsteps, base) before lane 0 overwrites them
+    cn = min(max_compacted - min(max_compacted, cbase), cn);
+    if (lane == 0) { sb.numsteps[i * 2 + 0] = cn; sb.numsteps[i * 2 + 1] = cbase; }
+    if (cn == 0) return;
+    const float* cin = sb.coords + (size_t)base * 7;
+    const __half* no = lb.network_output + (size_t)base * 4;
+    const float* rs = lb.ray_scratch + (size_t)i * 8;
+    const V3 rgb_ray = ld3(rs), target = ld3(rs + 3);
+    const V3 ray_o = ld3(sb.rays + (size_t)i * 6);
+
+    const LG lg = loss_and_gradient(target, rgb_ray, cfg.loss_type);
+    const float mean_loss = (lg.loss.x + lg.loss.y + lg.loss.z) / 3.0f;
+    if (lb.loss && lane == 0) lb.loss[i] = mean_loss / (float)n_rays_global;
+    const float loss_scale = cfg.loss_scale / (float)n_rays_global;
+    const float output_l2_reg = cfg.rgb_activation == ACT_EXPONENTIAL ? 1e-4f : 0.0f;
+    const float output_l1_reg_density = *mean_density < NERF_MIN_OPTICAL_THICKNESS ? 1e-4f : 0.0f;
+
+    V3 rgb_ray2 = v3(0, 0, 0); float T = 1.f;
+    __half* gout = lb.dloss_doutput + (size_t)cbase * 4;
+    float* cout = lb.coords_compacted + (size_t)cbase * 7;
+    for (uint32_t c0 = 0; c0 < cn; c0 += G) {
+        const uint32_t j = c0 + lane;
+        const bool valid = j < cn;
+        float o[4] = {0.f, 0.f, 0.f, 0.f}; V3 rgb = v3(0, 0, 0); float alpha = 0.f, dt = 0.f, depth = 0.f;
+        if (valid) {
+            float c[7];
+#pragma unroll
+            for (int k = 0; k < 7; ++k) { c[k] = __ldg(cin + (size_t)j * 7 + k); cout[(size_t)j * 7 + k] = c[k]; }
+            const V3 pos = unwarp_position(v3(c[0], c[1], c[2]), aabb);
+            depth = length3(pos - ray_o);
+            dt = unwarp_dt(c[3]);
+            load_out4(no + (size_t)j * 4, o);
+            rgb = v3(network_to_rgb(o[0], cfg.rgb_activation), network_to_rgb(o[1], cfg.rgb_activation), network_to_rgb(o[2], cfg.rgb_activation));
+            const float density = network_to_density(o[3], cfg.density_activation);
+            alpha = 1.f - expf(-density * dt);
+        }
+        float my_w = 0.f, my_T = 0.f; V3 my_r2 = v3(0, 0, 0);
+        const uint32_t n = min(G, cn - c0);
+        for (uint32_t k = 0; k < n; ++k) {
+            const float a = __shfl_sync(gmask, alpha, gshift + k);
+            const V3 r = v3(__shfl_sync(gmask, rgb.x, gshift + k), __shfl_sync(gmask, rgb.y, gshift + k), __shfl_sync(gmask, rgb.z, gshift + k));
+            const float weight = a * T;
+            rgb_ray2 = rgb_ray2 + weight * r;
+            T *= (1.f - a);
+            if (lane == k) { my_w = weight; my_T = T; my_r2 = rgb_ray2; }
+        }
+        if (valid) {
+            const V3 suffix = rgb_ray - my_r2;
+            const V3 dl_drgb = my_w * lg.grad;
+            const float g0 = loss_scale * (dl_drgb.x * network_to_rgb_derivative(o[0], cfg.rgb_activation) + fmaxf(0.0f, output_l2_reg * o[0]));
+            const float g1 = loss_scale * (dl_drgb.y * network_to_rgb_derivative(o[1], cfg.rgb_activation) + fmaxf(0.0f, output_l2_reg * o[1]));
+            const float g2 = loss_scale * (dl_drgb.z * network_to_rgb_derivative(o[2], cfg.rgb_activation) + fmaxf(0.0f, output_l2_reg * o[2]));
+            const float dd = network_to_density_derivative(o[3], cfg.density_activation);
+            const V3 tr = my_T * rgb - suffix;
+            const float dl_dmlp = dd * (dt * (lg.grad.x * tr.x + lg.grad.y * tr.y + lg.grad.z * tr.z));
+            const float g3 = loss_scale * dl_dmlp + (o[3] < 0.0f ? -output_l1_reg_density : 0.0f) + (o[3] > -10.0f && depth < cfg.near_distance ? 1e-4f : 0.0f);
+            __half2 h[2] = {__floats2half2_rn(g0, g1), __floats2half2_rn(g2, g3)};
+            *reinterpret_cast<uint2*>(gout + (size_t)j * 4) = *reinterpret_cast<uint2*>(h);
+        }
+    }
+}
+
 void nerf_compute_loss(cudaStream_t s, uint32_t n_rays, Aabb aabb, uint32_t n_rays_total, Pcg32 rng, uint32_t max_compacted, const LossConfig& cfg,
                        uint32_t n_images, const ImageMeta* metas, const float* mean_density_dev, uint32_t ray_offset, uint32_t n_rays_global,
                        const SamplerBuffers& sb, const LossBuffers& lb) {
     (void)n_rays_total;
     NGP_PROFILE_SCOPE(s, "loss", n_rays);
-    const uint32_t blocks = div_round_up(n_rays, SCAN_BLOCK);
-    loss_forward_kernel<<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, rng, cfg, n_images, metas, ray_offset, n_rays_global, sb, lb);
+    const uint32_t G = sb.lanes_per_ray == 1 ? 1u : (n_rays <= 2048 ? 32u : 8u);
+    const uint32_t blocks = div_round_up(n_rays, SCAN_BLOCK / G);
+    if (G == 32) loss_forward_group_kernel<32><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, rng, cfg, n_images, metas, ray_offset, n_rays_global, sb, lb);
+    else if (G == 8) loss_forward_group_kernel<8><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, rng, cfg, n_images, metas, ray_offset, n_rays_global, sb, lb);
+    else loss_forward_kernel<<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, rng, cfg, n_images, metas, ray_offset, n_rays_global, sb, lb);
     NGP_POST_LAUNCH();
     scan_block_totals_kernel<<<1, 1024, 0, s>>>(blocks, sb.block_steps, nullptr, &sb.counters[2], nullptr, false);
     NGP_POST_LAUNCH();
-    loss_backward_kernel<<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, max_compacted, cfg, mean_density_dev, n_rays_global, sb, lb);
+    if (G == 32) loss_backward_group_kernel<32><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, max_compacted, cfg, mean_density_dev, n_rays_global, sb, lb);
+    else if (G == 8) loss_backward_group_kernel<8><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, max_compacted, cfg, mean_density_dev, n_rays_global, sb, lb);
+    else loss_backward_kernel<<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, max_compacted, cfg, mean_density_dev, n_rays_global, sb, lb);
     NGP_POST_LAUNCH();
 }
 

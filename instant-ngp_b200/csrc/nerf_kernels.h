@@ -18,7 +18,7 @@ void nerf_update_bitfield(cudaStream_t s, const float* grid, uint32_t n_cascades
 struct SamplerBuffers {
     // per generated ray slot [n_rays]
     uint32_t* numsteps_all;     // pass-1 step count of ray i (0: no sample / masked)
-    uint32_t* block_steps;      // [n_blocks] per-block totals -> exclusive prefix after the scan
+    uint32_t* block_steps;      // [n_rays / 8 + 1] per-block totals (a block holds 256 / lanes_per_ray rays) -> exclusive prefix after the scan
     uint32_t* block_rays;       // [n_blocks]
     float* ray_tmp;             // [n_rays][8]: o(3), d unnormalised(3), startt, cone_angle (pass 1 -> pass 2)
     // compacted outputs
@@ -27,7 +27,9 @@ struct SamplerBuffers {
     uint32_t* numsteps;         // [n_rays][2] (numsteps, base)
     float* coords;              // [max_samples][7]
     uint32_t* counters;         // [0] ray_counter, [1] numsteps_counter (total, may exceed max_samples), [2] compacted counter
+    uint32_t lanes_per_ray;     // 0: choose from n_rays (nerf_sampler_lanes_per_ray); 1 / 8 / 32: forced (tests compare the variants)
 };
+uint32_t nerf_sampler_lanes_per_ray(uint32_t n_rays);
 void nerf_generate_training_samples(cudaStream_t s, uint32_t n_rays, Aabb aabb, uint32_t max_samples, uint32_t n_rays_total, Pcg32 rng,
                                     uint32_t n_images, const ImageMeta* metas, const uint8_t* bitfield, uint32_t max_mip,
                                     bool snap_to_pixel_centers, float cone_angle_constant, uint32_t ray_offset, uint32_t n_rays_global,

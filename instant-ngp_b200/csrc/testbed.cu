@@ -217,7 +217,7 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
     NGP_PROFILE_SCOPE(s, "train_nerf_step");
     const uint32_t max_samples = target * 16;   // "somewhat of a worst case" (:3873)
     const uint32_t R = m_rays_per_batch, max_rays = 1u << 18;
-    const uint32_t max_blocks = div_round_up(max_rays, 256);
+    const uint32_t max_blocks = max_rays / 8 + 1;   // 256 / lanes_per_ray rays per block, lanes_per_ray <= 32
     SamplerBuffers sb{};
     sb.numsteps_all = m_numsteps_all.get<uint32_t>(max_rays); sb.block_steps = m_block_steps.get<uint32_t>(max_blocks);
     sb.block_rays = m_block_rays.get<uint32_t>(max_blocks); sb.ray_tmp = m_ray_tmp.get<float>((size_t)max_rays * 8);
@@ -227,6 +227,7 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
     sb.coords = m_coords.get<float>((size_t)max_samples * 7);
     if (fresh_coords) NGP_CUDA_CHECK(cudaMemsetAsync(sb.coords, 0, (size_t)max_samples * 7 * 4, s));   // stale rows are fed to the network: keep them finite
     sb.counters = m_counters.get<uint32_t>(4);
+    sb.lanes_per_ray = sampler_lanes_per_ray;
     LossBuffers lb{};
     __half* mlp_out = m_mlp_out.get<__half>((size_t)max_samples * 4);
     lb.network_output = mlp_out; lb.dloss_doutput = m_dloss.get<__half>((size_t)target * 4);

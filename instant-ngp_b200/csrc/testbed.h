@@ -64,6 +64,7 @@ public:
     int loss_type = LOSS_L2, rgb_activation = ACT_LOGISTIC, density_activation = ACT_EXPONENTIAL;
     bool image_snap_to_pixel_centers = true, image_linear_colors = false, image_stratified = true;
     uint64_t seed = 1337;
+    uint32_t sampler_lanes_per_ray = 0;   // 0 = automatic; 1 / 8 / 32 force a marcher variant (parity tests)
     Aabb aabb{{0, 0, 0}, {1, 1, 1}}, render_aabb{{0, 0, 0}, {1, 1, 1}};
 
 private:

@@ -54,7 +54,7 @@ def _stream():
 _BOOL_OPTS = {"random_bg_color", "linear_colors", "snap_to_pixel_centers", "shall_train_encoding", "shall_train_network",
               "image_snap_to_pixel_centers", "image_linear_colors", "image_stratified"}
 _FLOAT_OPTS = {"near_distance", "density_grid_decay", "render_min_transmittance", "cone_angle_constant"}
-_INT_OPTS = {"loss_type", "rgb_activation", "density_activation", "seed"}
+_INT_OPTS = {"loss_type", "rgb_activation", "density_activation", "seed", "sampler_lanes_per_ray"}
 
 
 class Testbed:
@@ -68,8 +68,13 @@ class Testbed:
         object.__setattr__(self, "_dist", None)
 
     def __del__(self):
-        if getattr(self, "_h", None):
-            lib().ngp_testbed_destroy(self._h)
+        h = getattr(self, "_h", None)
+        if h and lib is not None:     # `lib` is already torn down when the interpreter exits
+            try:
+                lib().ngp_testbed_destroy(h)
+            except Exception:
+                pass
+            object.__setattr__(self, "_h", None)
 
     # ---- runtime knobs (def_readwrite members) ----
     def __getattr__(self, name):
