@@ -233,6 +233,48 @@ NGP_D void random_image_pos_training(Pcg32& rng, const int* res, bool snap, floa
     }
 }
 
+// Per-candidate arithmetic of the training walk.  FLAT = (cone_angle <= 1e-5 and max_cascade == 0), the aabb_scale 1 case:
+// the mip is always 0, the voxel resolution is the constant 128 and to/from_stepping_space are t / S and n * S, so the
+// generic helpers collapse to the expressions below — the same float operations in the same order (the division by the
+// power-of-two resolution is written as the exact multiplication by its inverse), hence the same bits.
+// t / MIN_CONE_STEPSIZE() without the generic IEEE-division sequence: q = t * (1/S) refined by one exact-residual FMA step
+// is the correctly rounded quotient; verified EXHAUSTIVELY against t / S for every float in [1e-30, 2048)
+// (tools/verify_fast_div.c: 1 157 627 904 values, 0 mismatches); outside that range the plain division is used.
+NGP_D float div_by_stepsize(float t) {
+    constexpr float S = SQRT3 / (float)NERF_STEPS, RS = 1.0f / S;
+    if (t >= 1e-30f && t < 2048.0f) { const float q = t * RS; return fmaf(fmaf(-q, S, t), RS, q); }
+    return t / S;
+}
+// where the counting walk leaves (t, dt) of the samples it finds: a fixed window per ray plus, for the few rays that
+// outgrow it, a whole-ray slot (NERF_STEPS entries) taken from a pool with one atomicAdd
+struct SampleLog {
+    float2* window; uint32_t cap; float2* pool; uint32_t pool_slots; uint32_t* pool_counter; uint32_t slot;
+    NGP_D float2* at(uint32_t k) const { return k < cap ? window + k : (slot < pool_slots ? pool + (size_t)slot * NERF_STEPS + k : nullptr); }
+};
+constexpr uint32_t NO_SLOT = 0xFFFFFFFFu;
+struct RayConst { V3 o, d, idir, hs; };   // hs = 0.5 * sign(d): the +-0.5 of distance_to_next_voxel
+NGP_D RayConst make_ray_const(V3 o, V3 d) {
+    return {o, d, v3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z), v3(0.5f * copysignf(1.0f, d.x), 0.5f * copysignf(1.0f, d.y), 0.5f * copysignf(1.0f, d.z))};
+}
+template <bool FLAT>
+NGP_D void candidate_dt_mip(float t, V3 pos, float cone, uint32_t max_mip, float& dt, uint32_t& mip, float& n) {
+    if (FLAT) { n = div_by_stepsize(t); dt = (n + 1.0f) * MIN_CONE_STEPSIZE() - t; mip = 0; }
+    else { n = 0.f; dt = calc_dt(t, cone); mip = mip_from_dt(dt, pos, max_mip); }
+}
+template <bool FLAT>
+NGP_D float candidate_skip(float t, float n, V3 pos, const RayConst& r, float cone, uint32_t mip) {
+    if (FLAT) {
+        const V3 p = (float)NERF_GRIDSIZE * (pos - v3(0.5f, 0.5f, 0.5f));
+        const float tx = (floorf(p.x + 0.5f + r.hs.x) - p.x) * r.idir.x;
+        const float ty = (floorf(p.y + 0.5f + r.hs.y) - p.y) * r.idir.y;
+        const float tz = (floorf(p.z + 0.5f + r.hs.z) - p.z) * r.idir.z;
+        const float dist = fmaxf(fminf(fminf(tx, ty), tz) * (1.0f / (float)NERF_GRIDSIZE), 0.0f);
+        const float nt = div_by_stepsize(t + dist);
+        return (n + ceilf(fmaxf(nt - n, 0.5f))) * MIN_CONE_STEPSIZE();
+    }
+    return advance_to_next_voxel(t, cone, pos, r.d, r.idir, mip);
+}
+
 template <bool WRITE>
 NGP_D uint32_t march_training_ray(V3 o, V3 d, float startt, float cone, const Aabb& aabb, const uint8_t* __restrict__ bitfield, uint32_t max_mip,
                                   uint32_t limit, float* __restrict__ coords) {
@@ -256,6 +298,87 @@ NGP_D uint32_t march_training_ray(V3 o, V3 d, float startt, float cone, const Aa
     return j;
 }
 
+// ---- one thread per ray, K look-ups in flight -----------------------------------------------------------------------
+// Same run speculation as the group marcher, but inside one thread: the chain is advanced K candidates ahead (registers),
+// the K occupancy bytes are fetched as independent loads (one exposed L2 latency per K candidates instead of one per
+// candidate), then resolved in order.  No redundant chain work, no cross-lane traffic; bit-identical by construction.
+template <bool WRITE, bool FLAT, uint32_t K>
+NGP_D uint32_t march_training_ray_ilp(V3 o, V3 d, float startt, float cone, const Aabb& aabb, const uint8_t* __restrict__ bitfield, uint32_t max_mip,
+                                      uint32_t limit, float* __restrict__ coords, SampleLog* log = nullptr) {
+    if (limit == 0) return 0;
+    const RayConst rc = make_ray_const(o, d);
+    const V3 wd = warp_direction(d);
+    uint32_t j = 0; float t = startt; bool step_mode = false;
+    while (true) {
+        float ts[K], dts[K]; uint32_t cell[K]; uint32_t n_valid = K;
+#pragma unroll
+        for (uint32_t k = 0; k < K; ++k) {
+            const V3 pos = ray_at(o, d, t);
+            if (n_valid == K && !aabb_contains(aabb, pos)) n_valid = k;
+            float dt, n; uint32_t mip;
+            candidate_dt_mip<FLAT>(t, pos, cone, max_mip, dt, mip, n);
+            const uint32_t idx = cascaded_grid_idx_at(pos, mip);
+            ts[k] = t; dts[k] = dt; cell[k] = idx == 0xFFFFFFFFu ? idx : idx + mip * NERF_GRID_N_CELLS;
+            t = step_mode ? t + dt : candidate_skip<FLAT>(t, n, pos, rc, cone, mip);
+        }
+        uint32_t occ_mask = 0;
+#pragma unroll
+        for (uint32_t k = 0; k < K; ++k) {
+            const bool look = k < n_valid && cell[k] != 0xFFFFFFFFu;
+            const uint32_t byte = look ? (uint32_t)__ldg(bitfield + (cell[k] >> 3)) : 0u;
+            occ_mask |= ((byte >> (cell[k] & 7u)) & 1u) << k;
+        }
+        if (step_mode) {
+            const uint32_t bad = ~occ_mask & ((1u << K) - 1u);
+            const uint32_t f = bad ? (uint32_t)__ffs((int)bad) - 1u : K;
+            const uint32_t n_emit = min(f, limit - j);
+            if (WRITE) {
+#pragma unroll
+                for (uint32_t k = 0; k < K; ++k) {
+                    if (k < n_emit) {
+                        float* c = coords + (size_t)(j + k) * 7;
+                        const V3 wp = warp_position(ray_at(o, d, ts[k]), aabb);
+                        c[0] = wp.x; c[1] = wp.y; c[2] = wp.z; c[3] = warp_dt(dts[k]); c[4] = wd.x; c[5] = wd.y; c[6] = wd.z;
+                    }
+                }
+            }
+            if (!WRITE && n_emit) {
+                if (j + n_emit > log->cap && log->slot == NO_SLOT) log->slot = atomicAdd(log->pool_counter, 1u);
+#pragma unroll
+                for (uint32_t k = 0; k < K; ++k) {
+                    float2* dst = k < n_emit ? log->at(j + k) : nullptr;
+                    if (dst) *dst = make_float2(ts[k], dts[k]);
+                }
+            }
+            j += n_emit;
+            if (j >= limit) break;
+            if (f == K) continue;                  // t already is candidate K
+            if (f >= n_valid) break;               // candidate f left the aabb
+            float tf = ts[0];
+#pragma unroll
+            for (uint32_t k = 1; k < K; ++k) if (k == f) tf = ts[k];
+            const V3 pos = ray_at(o, d, tf);
+            float dt, n; uint32_t mip;
+            candidate_dt_mip<FLAT>(tf, pos, cone, max_mip, dt, mip, n);
+            t = candidate_skip<FLAT>(tf, n, pos, rc, cone, mip);
+            step_mode = false;
+        } else {
+            if (occ_mask) {
+                const uint32_t f = (uint32_t)__ffs((int)occ_mask) - 1u;
+                float tf = ts[0];
+#pragma unroll
+                for (uint32_t k = 1; k < K; ++k) if (k == f) tf = ts[k];
+                t = tf; step_mode = true; continue;
+            }
+            if (n_valid < K) break;
+        }
+    }
+    return j;
+}
+
+constexpr uint32_t ILP_K = 8;
+
+template <bool FLAT>
 __global__ void __launch_bounds__(SCAN_BLOCK) sampler_count_kernel(uint32_t n_rays, Aabb aabb, Pcg32 rng, uint32_t n_images, const ImageMeta* __restrict__ metas,
                                                                    const uint8_t* __restrict__ bitfield, uint32_t max_mip, bool snap, float cone_angle_constant,
                                                                    uint32_t ray_offset, uint32_t n_rays_global, SamplerBuffers b) {
@@ -277,7 +400,9 @@ __global__ void __launch_bounds__(SCAN_BLOCK) sampler_count_kernel(uint32_t n_ra
             const float cone = cone_angle_constant;   // calc_cone_angle (:114-122)
             tmin = fmaxf(tmin, 0.0f);
             const float startt = advance_n_steps(tmin, cone, rng.next_float());
-            numsteps = march_training_ray<false>(o, d, startt, cone, aabb, bitfield, max_mip, NERF_STEPS, nullptr);
+            SampleLog log{b.sample_scratch + (size_t)i * b.scratch_per_ray, b.scratch_per_ray, b.sample_pool, b.pool_slots, &b.counters[3], NO_SLOT};
+            numsteps = march_training_ray_ilp<false, FLAT, ILP_K>(o, d, startt, cone, aabb, bitfield, max_mip, NERF_STEPS, nullptr, &log);
+            b.overflow_slot[i] = log.slot;
             float* rt = b.ray_tmp + (size_t)i * 8;
             rt[0] = o.x; rt[1] = o.y; rt[2] = o.z; rt[3] = du.x; rt[4] = du.y; rt[5] = du.z; rt[6] = startt; rt[7] = cone;
         }
@@ -289,6 +414,7 @@ __global__ void __launch_bounds__(SCAN_BLOCK) sampler_count_kernel(uint32_t n_ra
     if (threadIdx.x == 0) { b.block_steps[blockIdx.x] = total_steps; b.block_rays[blockIdx.x] = total_rays; }
 }
 
+template <bool FLAT>
 __global__ void __launch_bounds__(SCAN_BLOCK) sampler_write_kernel(uint32_t n_rays, Aabb aabb, uint32_t max_samples, const uint8_t* __restrict__ bitfield,
                                                                    uint32_t max_mip, SamplerBuffers b) {
     const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x;
@@ -307,7 +433,21 @@ __global__ void __launch_bounds__(SCAN_BLOCK) sampler_write_kernel(uint32_t n_ra
     float* r = b.rays + (size_t)ray_idx * 6;
     r[0] = o.x; r[1] = o.y; r[2] = o.z; r[3] = du.x; r[4] = du.y; r[5] = du.z;
     b.numsteps[ray_idx * 2 + 0] = numsteps; b.numsteps[ray_idx * 2 + 1] = base;
-    march_training_ray<true>(o, normalize3(du), rt[6], rt[7], aabb, bitfield, max_mip, numsteps, b.coords + (size_t)base * 7);
+    const V3 d = normalize3(du);
+    float* coords = b.coords + (size_t)base * 7;
+    const SampleLog log{b.sample_scratch + (size_t)i * b.scratch_per_ray, b.scratch_per_ray, b.sample_pool, b.pool_slots, nullptr,
+                        numsteps > b.scratch_per_ray ? b.overflow_slot[i] : NO_SLOT};
+    if (numsteps <= b.scratch_per_ray || log.slot < b.pool_slots) {
+        const V3 wd = warp_direction(d);
+        for (uint32_t k = 0; k < numsteps; ++k) {
+            const float2 td = *log.at(k);
+            const V3 wp = warp_position(ray_at(o, d, td.x), aabb);
+            float* c = coords + (size_t)k * 7;
+            c[0] = wp.x; c[1] = wp.y; c[2] = wp.z; c[3] = warp_dt(td.y); c[4] = wd.x; c[5] = wd.y; c[6] = wd.z;
+        }
+        return;
+    }
+    march_training_ray_ilp<true, FLAT, ILP_K>(o, d, rt[6], rt[7], aabb, bitfield, max_mip, numsteps, coords);
 }
 
 // ---- warp-cooperative marcher: G lanes per ray ------------------------------------------------------------------
@@ -318,24 +458,24 @@ __global__ void __launch_bounds__(SCAN_BLOCK) sampler_write_kernel(uint32_t n_ra
 // current run (occupied / empty) continues, lane k keeping candidate k, then test all G cells with one ballot.  The
 // candidates up to the first misprediction are exactly the serial walk's; the group restarts from there in the other
 // mode.  Every float operation is the serial one, so positions, sample counts and coordinates are bit-identical.
-template <uint32_t G, bool WRITE>
+template <uint32_t G, bool WRITE, bool FLAT>
 NGP_D uint32_t march_training_ray_group(V3 o, V3 d, float startt, float cone, const Aabb& aabb, const uint8_t* __restrict__ bitfield, uint32_t max_mip,
-                                        uint32_t limit, float* __restrict__ coords, uint32_t lane, uint32_t gshift, uint32_t gmask) {
+                                        uint32_t limit, float* __restrict__ coords, uint32_t lane, uint32_t gshift, uint32_t gmask, SampleLog* log = nullptr) {
     constexpr uint32_t FULL = G == 32 ? 0xffffffffu : ((1u << G) - 1u);
     if (limit == 0) return 0;
-    const V3 idir = v3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+    const RayConst rc = make_ray_const(o, d);
     const V3 wd = warp_direction(d);
     uint32_t j = 0; float t_base = startt; bool step_mode = false;
     while (true) {
-        float t = t_base, my_t = 0.f, my_dt = 0.f; V3 my_pos = v3(0.f, 0.f, 0.f); uint32_t my_mip = 0, n_valid = G;
+        float t = t_base, my_t = 0.f, my_dt = 0.f, my_n = 0.f; V3 my_pos = v3(0.f, 0.f, 0.f); uint32_t my_mip = 0, n_valid = G;
 #pragma unroll 1
         for (uint32_t it = 0; it < G; ++it) {
             const V3 pos = ray_at(o, d, t);
             if (!aabb_contains(aabb, pos)) { n_valid = it; break; }
-            const float dt = calc_dt(t, cone);
-            const uint32_t mip = mip_from_dt(dt, pos, max_mip);
-            if (it == lane) { my_t = t; my_dt = dt; my_pos = pos; my_mip = mip; }
-            t = step_mode ? t + dt : advance_to_next_voxel(t, cone, pos, d, idir, mip);
+            float dt, n; uint32_t mip;
+            candidate_dt_mip<FLAT>(t, pos, cone, max_mip, dt, mip, n);
+            if (it == lane) { my_t = t; my_dt = dt; my_n = n; my_pos = pos; my_mip = mip; }
+            t = step_mode ? t + dt : candidate_skip<FLAT>(t, n, pos, rc, cone, mip);
         }
         const bool occ = lane < n_valid && density_grid_occupied_at(my_pos, bitfield, my_mip);
         const uint32_t occ_mask = (__ballot_sync(gmask, occ) >> gshift) & FULL;
@@ -348,11 +488,20 @@ NGP_D uint32_t march_training_ray_group(V3 o, V3 d, float startt, float cone, co
                 const V3 wp = warp_position(my_pos, aabb);
                 c[0] = wp.x; c[1] = wp.y; c[2] = wp.z; c[3] = warp_dt(my_dt); c[4] = wd.x; c[5] = wd.y; c[6] = wd.z;
             }
+            if (!WRITE && n_emit) {
+                if (j + n_emit > log->cap && log->slot == NO_SLOT) {   // first sample beyond the window: take a pool slot (group-uniform)
+                    uint32_t sl = 0;
+                    if (lane == 0) sl = atomicAdd(log->pool_counter, 1u);
+                    log->slot = __shfl_sync(gmask, sl, gshift);
+                }
+                float2* dst = lane < n_emit ? log->at(j + lane) : nullptr;
+                if (dst) *dst = make_float2(my_t, my_dt);
+            }
             j += n_emit;
             if (j >= limit) break;
             if (f == G) { t_base = t; continue; }
             if (f >= n_valid) break;                                         // candidate f left the aabb: end of the walk
-            const float my_skip = advance_to_next_voxel(my_t, cone, my_pos, d, idir, my_mip);
+            const float my_skip = candidate_skip<FLAT>(my_t, my_n, my_pos, rc, cone, my_mip);
             t_base = __shfl_sync(gmask, my_skip, gshift + f);
             step_mode = false;
         } else {
@@ -364,7 +513,7 @@ NGP_D uint32_t march_training_ray_group(V3 o, V3 d, float startt, float cone, co
     return j;
 }
 
-template <uint32_t G>
+template <uint32_t G, bool FLAT>
 __global__ void __launch_bounds__(SCAN_BLOCK) sampler_count_group_kernel(uint32_t n_rays, Aabb aabb, Pcg32 rng, uint32_t n_images, const ImageMeta* __restrict__ metas,
                                                                          const uint8_t* __restrict__ bitfield, uint32_t max_mip, bool snap, float cone_angle_constant,
                                                                          uint32_t ray_offset, uint32_t n_rays_global, SamplerBuffers b) {
@@ -389,7 +538,9 @@ __global__ void __launch_bounds__(SCAN_BLOCK) sampler_count_group_kernel(uint32_
             const float cone = cone_angle_constant;
             tmin = fmaxf(tmin, 0.0f);
             const float startt = advance_n_steps(tmin, cone, rng.next_float());
-            numsteps = march_training_ray_group<G, false>(o, d, startt, cone, aabb, bitfield, max_mip, NERF_STEPS, nullptr, lane, gshift, gmask);
+            SampleLog log{b.sample_scratch + (size_t)i * b.scratch_per_ray, b.scratch_per_ray, b.sample_pool, b.pool_slots, &b.counters[3], NO_SLOT};
+            numsteps = march_training_ray_group<G, false, FLAT>(o, d, startt, cone, aabb, bitfield, max_mip, NERF_STEPS, nullptr, lane, gshift, gmask, &log);
+            if (lane == 0) b.overflow_slot[i] = log.slot;
             if (lane == 0) {
                 float* rt = b.ray_tmp + (size_t)i * 8;
                 rt[0] = o.x; rt[1] = o.y; rt[2] = o.z; rt[3] = du.x; rt[4] = du.y; rt[5] = du.z; rt[6] = startt; rt[7] = cone;
@@ -404,7 +555,7 @@ __global__ void __launch_bounds__(SCAN_BLOCK) sampler_count_group_kernel(uint32_
     if (threadIdx.x == 0) { b.block_steps[blockIdx.x] = total_steps; b.block_rays[blockIdx.x] = total_rays; }
 }
 
-template <uint32_t G>
+template <uint32_t G, bool FLAT>
 __global__ void __launch_bounds__(SCAN_BLOCK) sampler_write_group_kernel(uint32_t n_rays, Aabb aabb, uint32_t max_samples, const uint8_t* __restrict__ bitfield,
                                                                          uint32_t max_mip, SamplerBuffers b) {
     constexpr uint32_t RPB = SCAN_BLOCK / G;
@@ -429,12 +580,26 @@ __global__ void __launch_bounds__(SCAN_BLOCK) sampler_write_group_kernel(uint32_
         r[0] = o.x; r[1] = o.y; r[2] = o.z; r[3] = du.x; r[4] = du.y; r[5] = du.z;
         b.numsteps[ray_idx * 2 + 0] = numsteps; b.numsteps[ray_idx * 2 + 1] = base;
     }
-    march_training_ray_group<G, true>(o, normalize3(du), rt[6], rt[7], aabb, bitfield, max_mip, numsteps, b.coords + (size_t)base * 7, lane, gshift, gmask);
+    const V3 d = normalize3(du);
+    float* coords = b.coords + (size_t)base * 7;
+    const SampleLog log{b.sample_scratch + (size_t)i * b.scratch_per_ray, b.scratch_per_ray, b.sample_pool, b.pool_slots, nullptr,
+                        numsteps > b.scratch_per_ray ? b.overflow_slot[i] : NO_SLOT};
+    if (numsteps <= b.scratch_per_ray || log.slot < b.pool_slots) {   // the counting walk left (t, dt) of every sample: no second traversal
+        const V3 wd = warp_direction(d);
+        for (uint32_t k = lane; k < numsteps; k += G) {
+            const float2 td = *log.at(k);
+            const V3 wp = warp_position(ray_at(o, d, td.x), aabb);
+            float* c = coords + (size_t)k * 7;
+            c[0] = wp.x; c[1] = wp.y; c[2] = wp.z; c[3] = warp_dt(td.y); c[4] = wd.x; c[5] = wd.y; c[6] = wd.z;
+        }
+        return;
+    }
+    march_training_ray_group<G, true, FLAT>(o, d, rt[6], rt[7], aabb, bitfield, max_mip, numsteps, coords, lane, gshift, gmask);
 }
 
 // lanes per ray: few long rays -> a whole warp per ray; the usual tens of thousands of rays -> 8 lanes; beyond that the
 // lock-step chain's redundancy costs more issue slots than the look-up latency it hides -> one thread per ray
-uint32_t nerf_sampler_lanes_per_ray(uint32_t n_rays) { return n_rays <= 2048 ? 32u : (n_rays <= 65536 ? 8u : 1u); }
+uint32_t nerf_sampler_lanes_per_ray(uint32_t n_rays) { return n_rays <= 1024 ? 32u : (n_rays <= 65536 ? 8u : 1u); }   // measured: tools/phase_profile.py
 
 void nerf_generate_training_samples(cudaStream_t s, uint32_t n_rays, Aabb aabb, uint32_t max_samples, uint32_t n_rays_total, Pcg32 rng,
                                     uint32_t n_images, const ImageMeta* metas, const uint8_t* bitfield, uint32_t max_mip, bool snap,
@@ -442,16 +607,26 @@ void nerf_generate_training_samples(cudaStream_t s, uint32_t n_rays, Aabb aabb, 
     (void)n_rays_total;
     NGP_PROFILE_SCOPE(s, "sampler", n_rays);
     const uint32_t G = b.lanes_per_ray ? b.lanes_per_ray : nerf_sampler_lanes_per_ray(n_rays);
+    NGP_CHECK(G == 1 || G == 4 || G == 8 || G == 32, "sampler_lanes_per_ray must be 0 (automatic), 1, 4, 8 or 32");
+    const bool flat = cone_angle_constant <= 1e-5f && max_mip == 0;
     const uint32_t blocks = div_round_up(n_rays, SCAN_BLOCK / G);
-    if (G == 32) sampler_count_group_kernel<32><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, rng, n_images, metas, bitfield, max_mip, snap, cone_angle_constant, ray_offset, n_rays_global, b);
-    else if (G == 8) sampler_count_group_kernel<8><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, rng, n_images, metas, bitfield, max_mip, snap, cone_angle_constant, ray_offset, n_rays_global, b);
-    else sampler_count_kernel<<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, rng, n_images, metas, bitfield, max_mip, snap, cone_angle_constant, ray_offset, n_rays_global, b);
+#define NGP_SAMPLER_COUNT(GG, FF) sampler_count_group_kernel<GG, FF><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, rng, n_images, metas, bitfield, max_mip, snap, cone_angle_constant, ray_offset, n_rays_global, b)
+#define NGP_SAMPLER_WRITE(GG, FF) sampler_write_group_kernel<GG, FF><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, max_samples, bitfield, max_mip, b)
+#define NGP_SAMPLER_DISPATCH(WHAT)                                                       \
+    do {                                                                                 \
+        if (G == 32) { if (flat) WHAT(32, true); else WHAT(32, false); }                 \
+        else if (G == 8) { if (flat) WHAT(8, true); else WHAT(8, false); }               \
+        else if (G == 4) { if (flat) WHAT(4, true); else WHAT(4, false); }               \
+    } while (0)
+    if (G == 1) { if (flat) sampler_count_kernel<true><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, rng, n_images, metas, bitfield, max_mip, snap, cone_angle_constant, ray_offset, n_rays_global, b);
+                  else sampler_count_kernel<false><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, rng, n_images, metas, bitfield, max_mip, snap, cone_angle_constant, ray_offset, n_rays_global, b); }
+    else NGP_SAMPLER_DISPATCH(NGP_SAMPLER_COUNT);
     NGP_POST_LAUNCH();
     scan_block_totals_kernel<<<1, 1024, 0, s>>>(blocks, b.block_steps, b.block_rays, &b.counters[1], nullptr, false);
     NGP_POST_LAUNCH();
-    if (G == 32) sampler_write_group_kernel<32><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, max_samples, bitfield, max_mip, b);
-    else if (G == 8) sampler_write_group_kernel<8><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, max_samples, bitfield, max_mip, b);
-    else sampler_write_kernel<<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, max_samples, bitfield, max_mip, b);
+    if (G == 1) { if (flat) sampler_write_kernel<true><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, max_samples, bitfield, max_mip, b);
+                  else sampler_write_kernel<false><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, max_samples, bitfield, max_mip, b); }
+    else NGP_SAMPLER_DISPATCH(NGP_SAMPLER_WRITE);
     NGP_POST_LAUNCH();
 }
 

@@ -26,8 +26,11 @@ struct SamplerBuffers {
     float* rays;                // [n_rays][6] unnormalised o,d
     uint32_t* numsteps;         // [n_rays][2] (numsteps, base)
     float* coords;              // [max_samples][7]
-    uint32_t* counters;         // [0] ray_counter, [1] numsteps_counter (total, may exceed max_samples), [2] compacted counter
-    uint32_t lanes_per_ray;     // 0: choose from n_rays (nerf_sampler_lanes_per_ray); 1 / 8 / 32: forced (tests compare the variants)
+    uint32_t* counters;         // [0] ray_counter, [1] numsteps_counter (total, may exceed max_samples), [2] compacted counter, [3] pool slots taken
+    float2* sample_scratch;     // [n_rays][scratch_per_ray] (t, dt) of the samples found by the counting walk
+    uint32_t scratch_per_ray;   // window per ray; rays that outgrow it continue in a pool slot (NERF_STEPS entries each)
+    float2* sample_pool; uint32_t pool_slots; uint32_t* overflow_slot;   // [pool_slots][NERF_STEPS]; [n_rays] slot of ray i or NO_SLOT; counters[3] = slots taken
+    uint32_t lanes_per_ray;     // 0: choose from n_rays (nerf_sampler_lanes_per_ray); 1 / 4 / 8 / 32: forced (tests compare the variants)
 };
 uint32_t nerf_sampler_lanes_per_ray(uint32_t n_rays);
 void nerf_generate_training_samples(cudaStream_t s, uint32_t n_rays, Aabb aabb, uint32_t max_samples, uint32_t n_rays_total, Pcg32 rng,

@@ -228,6 +228,9 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
     if (fresh_coords) NGP_CUDA_CHECK(cudaMemsetAsync(sb.coords, 0, (size_t)max_samples * 7 * 4, s));   // stale rows are fed to the network: keep them finite
     sb.counters = m_counters.get<uint32_t>(4);
     sb.lanes_per_ray = sampler_lanes_per_ray;
+    sb.sample_scratch = m_sample_scratch.get<float2>(max_samples);
+    sb.scratch_per_ray = std::min<uint32_t>(NERF_STEPS, max_samples / R);
+    sb.pool_slots = 4096; sb.sample_pool = m_sample_pool.get<float2>((size_t)sb.pool_slots * NERF_STEPS); sb.overflow_slot = m_overflow_slot.get<uint32_t>(max_rays);
     LossBuffers lb{};
     __half* mlp_out = m_mlp_out.get<__half>((size_t)max_samples * 4);
     lb.network_output = mlp_out; lb.dloss_doutput = m_dloss.get<__half>((size_t)target * 4);

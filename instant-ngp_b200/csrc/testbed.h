@@ -92,7 +92,7 @@ private:
     uint32_t m_rays_per_batch = 1u << 12, m_n_rays_total = 0, m_measured = 0, m_measured_before = 0;
     // per-step scratch
     DeviceBuffer m_numsteps_all, m_block_steps, m_block_rays, m_ray_tmp, m_ray_indices, m_rays, m_numsteps, m_coords, m_counters, m_mlp_out, m_dloss,
-        m_coords_compacted, m_loss, m_ray_scratch, m_compacted_numsteps, m_loss_sum;
+        m_coords_compacted, m_loss, m_ray_scratch, m_compacted_numsteps, m_loss_sum, m_sample_scratch, m_sample_pool, m_overflow_slot;
     // image mode
     DeviceBuffer m_image; int m_image_w = 0, m_image_h = 0; DeviceBuffer m_img_pos, m_img_target, m_img_out, m_img_dl, m_img_loss;
     // render scratch
