@@ -9,6 +9,8 @@
 //   as the reference's fp16 activations) and writes its row as 16-byte chunks into the next layer's operand tile.
 #include "ngp_internal.h"
 #include "tc05.cuh"
+#include <cstdio>
+#include <cstdlib>
 
 namespace ngp {
 using namespace tc;
@@ -107,7 +109,7 @@ struct FwdParams {
 template <uint32_t PW, uint32_t DH, uint32_t RH, int MODE>
 struct FwdSmem {
     // byte offsets from the 128 B aligned dynamic smem base
-    uint32_t wd[DH + 1], wr[RH + 1], x0[2], ha, hb, r0, bars, total;
+    uint32_t wd[DH + 1], wr[RH + 1], x0, ha, r0, bars, total;
     __host__ __device__ FwdSmem() {
         SmemCursor c;
         wd[0] = c.take(MLP_WIDTH * PW * 2);
@@ -119,8 +121,8 @@ struct FwdSmem {
             wr[RH] = c.take(MLP_OUT_PAD * MLP_WIDTH * 2);
             r0 = c.take(TILE_ROWS * 32 * 2);
         } else { for (uint32_t l = 0; l <= RH; ++l) wr[l] = 0; r0 = 0; }
-        x0[0] = c.take(TILE_ROWS * PW * 2); x0[1] = c.take(TILE_ROWS * PW * 2);
-        ha = c.take(TILE_ROWS * MLP_WIDTH * 2); hb = c.take(TILE_ROWS * MLP_WIDTH * 2);
+        x0 = c.take(TILE_ROWS * PW * 2);
+        ha = c.take(TILE_ROWS * MLP_WIDTH * 2);   // one hidden-activation tile, rewritten in place layer after layer
         bars = c.take(64);
         total = c.off + 128;
     }
@@ -163,42 +165,38 @@ __global__ void __launch_bounds__(128) mlp_forward_kernel(const FwdParams p) {
     const uint32_t tmem_row = tmem_base + ((warp * 32u) << 16);   // this warp's lane quadrant, column 0
 
     const uint32_t sbase = smem_u32(smem);
-    const Operand X0[2] = {{sbase + L.x0[0], PW}, {sbase + L.x0[1], PW}};
-    const Operand HA = {sbase + L.ha, MLP_WIDTH}, HB = {sbase + L.hb, MLP_WIDTH}, R0 = {sbase + L.r0, 32};
+    const Operand X0 = {sbase + L.x0, PW};
+    const Operand HA = {sbase + L.ha, MLP_WIDTH}, R0 = {sbase + L.r0, 32};
     __half* ha = reinterpret_cast<__half*>(smem + L.ha);
-    __half* hb = reinterpret_cast<__half*>(smem + L.hb);
     __half* r0 = reinterpret_cast<__half*>(smem + L.r0);
     constexpr uint32_t X_BYTES = TILE_ROWS * PW * 2;
 
     StageSync stage{bar_mma, 0};
-    uint32_t full_parity[2] = {0, 0};
-    uint32_t it = 0;
+    uint32_t full_parity = 0;
     if (tid == 0 && blockIdx.x < p.n_tiles) {
         mbar_expect_tx(&bar_full[0], X_BYTES);
-        bulk_g2s(smem + L.x0[0], p.enc + (size_t)blockIdx.x * TILE_ROWS * PW, X_BYTES, &bar_full[0]);
+        bulk_g2s(smem + L.x0, p.enc + (size_t)blockIdx.x * TILE_ROWS * PW, X_BYTES, &bar_full[0]);
     }
-    for (uint32_t tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++it) {
-        const uint32_t buf = it & 1;
+    for (uint32_t tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
         const uint32_t next = tile + gridDim.x;
-        if (tid == 0 && next < p.n_tiles) {   // prefetch the next input tile (its buffer was released one iteration ago)
-            mbar_expect_tx(&bar_full[buf ^ 1], X_BYTES);
-            bulk_g2s(smem + L.x0[buf ^ 1], p.enc + (size_t)next * TILE_ROWS * PW, X_BYTES, &bar_full[buf ^ 1]);
-        }
         const uint32_t row_g = tile * TILE_ROWS + tid;
         float dir[3] = {0.f, 0.f, 0.f};
         if (MODE == MODE_NERF) { const float* c = p.coords + (size_t)row_g * 7 + 4; dir[0] = __ldg(c); dir[1] = __ldg(c + 1); dir[2] = __ldg(c + 2); }
-        mbar_wait(&bar_full[buf], full_parity[buf]); full_parity[buf] ^= 1u;
+        mbar_wait(&bar_full[0], full_parity); full_parity ^= 1u;
 
         // ---- density / plain network ----
-        stage.run([&] { gemm_act_wT<64>(tmem_base, X0[buf], 0, Operand{sbase + L.wd[0], PW}, PW); });
-        epilogue_to_smem<64, true>(tmem_row, ha, MLP_WIDTH, 0, tid);
-        bool in_a = true;
-        for (uint32_t l = 1; l < DH; ++l) {
-            stage.run([&] { gemm_act_wT<64>(tmem_base, in_a ? HA : HB, 0, Operand{sbase + L.wd[l], MLP_WIDTH}, MLP_WIDTH); });
-            epilogue_to_smem<64, true>(tmem_row, in_a ? hb : ha, MLP_WIDTH, 0, tid);
-            in_a = !in_a;
+        stage.run([&] { gemm_act_wT<64>(tmem_base, X0, 0, Operand{sbase + L.wd[0], PW}, PW); });
+        // the first layer's MMAs have completed: the input tile is free -> fetch the next one under the remaining layers
+        if (tid == 0 && next < p.n_tiles) {
+            mbar_expect_tx(&bar_full[0], X_BYTES);
+            bulk_g2s(smem + L.x0, p.enc + (size_t)next * TILE_ROWS * PW, X_BYTES, &bar_full[0]);
         }
-        stage.run([&] { gemm_act_wT<16>(tmem_base, in_a ? HA : HB, 0, Operand{sbase + L.wd[DH], MLP_WIDTH}, MLP_WIDTH); });
+        epilogue_to_smem<64, true>(tmem_row, ha, MLP_WIDTH, 0, tid);
+        for (uint32_t l = 1; l < DH; ++l) {   // hidden activations are rewritten in place: the MMAs that read them have completed
+            stage.run([&] { gemm_act_wT<64>(tmem_base, HA, 0, Operand{sbase + L.wd[l], MLP_WIDTH}, MLP_WIDTH); });
+            epilogue_to_smem<64, true>(tmem_row, ha, MLP_WIDTH, 0, tid);
+        }
+        stage.run([&] { gemm_act_wT<16>(tmem_base, HA, 0, Operand{sbase + L.wd[DH], MLP_WIDTH}, MLP_WIDTH); });
         float dout[16];
         tmem_ld16(tmem_row, dout); tmem_wait_ld();
         if (MODE == MODE_DENSITY) { p.out[row_g] = __float2half_rn(dout[0]); continue; }
@@ -216,13 +214,11 @@ __global__ void __launch_bounds__(128) mlp_forward_kernel(const FwdParams p) {
         *reinterpret_cast<uint4*>(r0 + blk8_chunk_offset(tid, 3, 32)) = pack8(sh + 8, false);
         stage.run([&] { gemm_act_wT<64>(tmem_base, R0, 0, Operand{sbase + L.wr[0], 32}, 32); });
         epilogue_to_smem<64, true>(tmem_row, ha, MLP_WIDTH, 0, tid);
-        in_a = true;
         for (uint32_t l = 1; l < RH; ++l) {
-            stage.run([&] { gemm_act_wT<64>(tmem_base, in_a ? HA : HB, 0, Operand{sbase + L.wr[l], MLP_WIDTH}, MLP_WIDTH); });
-            epilogue_to_smem<64, true>(tmem_row, in_a ? hb : ha, MLP_WIDTH, 0, tid);
-            in_a = !in_a;
+            stage.run([&] { gemm_act_wT<64>(tmem_base, HA, 0, Operand{sbase + L.wr[l], MLP_WIDTH}, MLP_WIDTH); });
+            epilogue_to_smem<64, true>(tmem_row, ha, MLP_WIDTH, 0, tid);
         }
-        stage.run([&] { gemm_act_wT<16>(tmem_base, in_a ? HA : HB, 0, Operand{sbase + L.wr[RH], MLP_WIDTH}, MLP_WIDTH); });
+        stage.run([&] { gemm_act_wT<16>(tmem_base, HA, 0, Operand{sbase + L.wr[RH], MLP_WIDTH}, MLP_WIDTH); });
         float rgb[16];
         tmem_ld16(tmem_row, rgb); tmem_wait_ld();
         __half2 o2[2] = {__floats2half2_rn(rgb[0], rgb[1]), __halves2half2(__float2half_rn(rgb[2]), sigma)};
@@ -493,20 +489,26 @@ static int sm_count() {
     return n;
 }
 
+// CTAs per SM of a persistent fused-MLP kernel.  cudaOccupancyMaxActiveBlocksPerMultiprocessor reports 1 for any kernel
+// that allocates tensor memory (measured on B200, driver 580), although the SM co-schedules such CTAs as long as their
+// TMEM columns (512 per SM), shared memory (227 KB + 1 KB reserved per CTA) and threads fit — so the limit is computed here.
 template <class K>
-static uint32_t persistent_grid(K kernel, uint32_t smem_bytes, uint32_t n_tiles) {
+static uint32_t persistent_grid(K kernel, uint32_t smem_bytes, uint32_t tmem_cols, uint32_t n_tiles) {
     NGP_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
-    int per_sm = 0;
-    NGP_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, 128, smem_bytes));
-    NGP_CHECK(per_sm >= 1, "fused MLP kernel does not fit on an SM");
-    return std::min<uint32_t>(n_tiles, (uint32_t)per_sm * (uint32_t)sm_count());
+    NGP_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
+    NGP_CHECK(smem_bytes + 1024 <= 227 * 1024, "fused MLP kernel does not fit on an SM");
+    uint32_t per_sm = std::min<uint32_t>((227u * 1024u) / (smem_bytes + 1024u), 512u / tmem_cols);
+    per_sm = std::max(1u, std::min(per_sm, 8u));
+    if (const char* e = getenv("NGP_MLP_CTAS_PER_SM")) per_sm = (uint32_t)std::max(1, atoi(e));
+    if (getenv("NGP_DEBUG")) fprintf(stderr, "[ngp] fused MLP kernel: smem %u B, tmem %u cols, %u CTAs/SM, %u tiles\n", smem_bytes, tmem_cols, per_sm, n_tiles);
+    return std::min<uint32_t>(n_tiles, per_sm * (uint32_t)sm_count());
 }
 
 template <uint32_t PW, uint32_t DH, uint32_t RH, int MODE>
 static void launch_fwd(cudaStream_t s, const FwdParams& p) {
     const FwdSmem<PW, DH, RH, MODE> L;
     auto k = mlp_forward_kernel<PW, DH, RH, MODE>;
-    const uint32_t grid = persistent_grid(k, L.total, p.n_tiles);
+    const uint32_t grid = persistent_grid(k, L.total, 64, p.n_tiles);
     k<<<grid, 128, L.total, s>>>(p);
     NGP_POST_LAUNCH();
 }
@@ -516,11 +518,11 @@ static void launch_bwd(cudaStream_t s, const BwdParams& p) {
     const BwdCfg<PW, DH, RH, MODE> L;
     if (p.dL_denc) {
         auto k = mlp_backward_kernel<PW, DH, RH, MODE, true>;
-        const uint32_t grid = persistent_grid(k, L.total, p.n_tiles);
+        const uint32_t grid = persistent_grid(k, L.total, BwdCfg<PW, DH, RH, MODE>::TMEM_COLS, p.n_tiles);
         k<<<grid, 128, L.total, s>>>(p);
     } else {
         auto k = mlp_backward_kernel<PW, DH, RH, MODE, false>;
-        const uint32_t grid = persistent_grid(k, L.total, p.n_tiles);
+        const uint32_t grid = persistent_grid(k, L.total, BwdCfg<PW, DH, RH, MODE>::TMEM_COLS, p.n_tiles);
         k<<<grid, 128, L.total, s>>>(p);
     }
     NGP_POST_LAUNCH();
