@@ -101,18 +101,59 @@ NGP_D void accumulate(float* acc, float w, typename Feat<F>::T raw) {
     for (uint32_t f = 0; f < F; ++f) acc[f] = fmaf(w, __half2float(h[f]), acc[f]);
 }
 
+// All 2^D corner indices and weights of one level with the per-axis work factored out: two candidate cells per axis
+// (c, c+1) give two hash terms / dense offsets and two weights per axis; a corner combines one of each.  The products are
+// formed in the reference order ((wx*wy)*wz), so weights and indices are bit-identical to corner_index().
+template <uint32_t D>
+struct LevelCorners {
+    uint32_t term[D][2]; float wt[D][2]; uint32_t size; bool hashed;
+    NGP_D LevelCorners(const GridLayout& g, uint32_t level, const float* __restrict__ x) {
+        const float scale = g.scales[level];
+        size = g.sizes[level]; hashed = (g.hashed_mask >> level) & 1u;
+#pragma unroll
+        for (uint32_t d = 0; d < D; ++d) {
+            const float p = fmaf(scale, x[d], 0.5f), fl = floorf(p);
+            const uint32_t c = (uint32_t)(int)fl; const float f = p - fl;
+            wt[d][0] = 1.0f - f; wt[d][1] = f;
+            const uint32_t mul = hashed ? (d == 0 ? 1u : (d == 1 ? GRID_PRIME_1 : GRID_PRIME_2)) : g.dense_stride[level][d];
+            term[d][0] = c * mul; term[d][1] = (c + 1u) * mul;
+        }
+    }
+    NGP_D uint32_t index(uint32_t corner) const {
+        uint32_t i;
+        if (hashed) {
+            i = term[0][corner & 1u];
+            if (D > 1) i ^= term[1][(corner >> 1) & 1u];
+            if (D > 2) i ^= term[2][(corner >> 2) & 1u];
+            return i & (size - 1u);
+        }
+        i = term[0][corner & 1u];
+        if (D > 1) i += term[1][(corner >> 1) & 1u];
+        if (D > 2) i += term[2][(corner >> 2) & 1u];
+        return i >= size ? i % size : i;
+    }
+    NGP_D float weight(uint32_t corner) const {
+        float w = wt[0][corner & 1u];
+        if (D > 1) w *= wt[1][(corner >> 1) & 1u];
+        if (D > 2) w *= wt[2][(corner >> 2) & 1u];
+        return w;
+    }
+};
+
+// Mapping: blockIdx.y = 8-feature chunk (8/F consecutive levels), so the level — and with it every constant-bank read of
+// the layout and the hashed/dense branch — is uniform across the block; threads are consecutive points, so a warp's
+// 16-byte stores fill four whole 128-byte core matrices of the blk8 output.
 template <uint32_t D, uint32_t F>
 __global__ void __launch_bounds__(256) grid_forward_kernel(const GridLayout g, const __half* __restrict__ table, const float* __restrict__ x,
                                                            uint32_t x_stride, uint32_t n, __half* __restrict__ y, int y_layout) {
     constexpr uint32_t LPC = 8 / F;          // levels per 8-feature chunk
     constexpr uint32_t NC = 1u << D;
-    const uint32_t chunks = g.padded_width / 8;
-    // consecutive threads: 8 rows x `chunks` chunks, rows fastest, so a warp's 16 B stores fill whole 128 B core matrices
-    const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
-    const uint32_t group = tid / (8 * chunks), in_group = tid % (8 * chunks);
-    const uint32_t row = group * 8 + (in_group & 7), chunk = in_group >> 3;
+    const uint32_t row = blockIdx.x * blockDim.x + threadIdx.x, chunk = blockIdx.y;
     if (row >= n) return;
     const float* xp = x + (size_t)row * x_stride;
+    float xs[D];
+#pragma unroll
+    for (uint32_t d = 0; d < D; ++d) xs[d] = __ldg(xp + d);
     float acc[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) acc[i] = 0.0f;
@@ -120,13 +161,13 @@ __global__ void __launch_bounds__(256) grid_forward_kernel(const GridLayout g, c
     for (uint32_t li = 0; li < LPC; ++li) {
         const uint32_t level = chunk * LPC + li;
         if (level >= g.n_levels) break;
-        const Cell<D> cell = locate<D>(xp, g.scales[level]);
+        const LevelCorners<D> lc(g, level, xs);
         const typename Feat<F>::T* t = reinterpret_cast<const typename Feat<F>::T*>(table) + g.offsets[level];
-        typename Feat<F>::T raw[NC]; float w[NC];
+        typename Feat<F>::T raw[NC];
 #pragma unroll
-        for (uint32_t k = 0; k < NC; ++k) raw[k] = __ldg(t + corner_index<D>(g, level, cell, k, w[k]));
+        for (uint32_t k = 0; k < NC; ++k) raw[k] = __ldg(t + lc.index(k));
 #pragma unroll
-        for (uint32_t k = 0; k < NC; ++k) accumulate<F>(acc + li * F, w[k], raw[k]);
+        for (uint32_t k = 0; k < NC; ++k) accumulate<F>(acc + li * F, lc.weight(k), raw[k]);
     }
     __half2 o[4];
 #pragma unroll
@@ -147,16 +188,16 @@ __global__ void __launch_bounds__(256) grid_backward_kernel(const GridLayout g, 
                                                             const __half* __restrict__ dy, int dy_layout, __half* __restrict__ grad) {
     constexpr uint32_t LPC = 8 / F;
     constexpr uint32_t NC = 1u << D;
-    const uint32_t chunks = g.padded_width / 8;
-    const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
-    const uint32_t group = tid / (8 * chunks), in_group = tid % (8 * chunks);
-    const uint32_t row = group * 8 + (in_group & 7), chunk = in_group >> 3;
+    const uint32_t row = blockIdx.x * blockDim.x + threadIdx.x, chunk = blockIdx.y;
     if (row >= n) return;
     size_t off = (dy_layout == LAYOUT_BLK8) ? blk8_chunk_offset(row, chunk, g.padded_width) : (size_t)row * g.padded_width + chunk * 8;
     const uint4 raw = __ldg(reinterpret_cast<const uint4*>(dy + off));
     if ((raw.x | raw.y | raw.z | raw.w) == 0u) return;   // padding rows / untouched levels contribute nothing
     const __half* dh = reinterpret_cast<const __half*>(&raw);
     const float* xp = x + (size_t)row * x_stride;
+    float xs[D];
+#pragma unroll
+    for (uint32_t d = 0; d < D; ++d) xs[d] = __ldg(xp + d);
 #pragma unroll
     for (uint32_t li = 0; li < LPC; ++li) {
         const uint32_t level = chunk * LPC + li;
@@ -165,12 +206,12 @@ __global__ void __launch_bounds__(256) grid_backward_kernel(const GridLayout g, 
 #pragma unroll
         for (uint32_t f = 0; f < F; ++f) { d[f] = __half2float(dh[li * F + f]); any |= d[f] != 0.0f; }
         if (!any) continue;
-        const Cell<D> cell = locate<D>(xp, g.scales[level]);
+        const LevelCorners<D> lc(g, level, xs);
         __half* gl = grad + (size_t)g.offsets[level] * F;
 #pragma unroll
         for (uint32_t k = 0; k < NC; ++k) {
-            float w; const uint32_t idx = corner_index<D>(g, level, cell, k, w);
-            __half* p = gl + (size_t)idx * F;
+            const float w = lc.weight(k);
+            __half* p = gl + (size_t)lc.index(k) * F;
             if (F == 1) atomicAdd(p, __float2half_rn(w * d[0]));
             else if (F == 2) red_add_h2(p, w * d[0], w * d[1]);
             else if (F == 4) red_add_h4(p, w * d[0], w * d[1], w * d[2], w * d[3]);
@@ -267,8 +308,7 @@ void grid_forward(cudaStream_t s, const GridLayout& g, const __half* table, cons
                   __half* y, int y_layout) {
     if (n == 0) return;
     NGP_PROFILE_SCOPE(s, "grid_forward", n);
-    const uint32_t threads = (uint32_t)next_multiple(n, 8) * (g.padded_width / 8);
-    const uint32_t blocks = div_round_up(threads, 256);
+    const dim3 blocks(div_round_up(n, 256), g.padded_width / 8, 1);
     GRID_DISPATCH(grid_forward_kernel, g, table, x, x_stride, n, y, y_layout);
 }
 
@@ -276,8 +316,7 @@ void grid_backward(cudaStream_t s, const GridLayout& g, const float* x, uint32_t
                    int dy_layout, __half* grad) {
     if (n == 0) return;
     NGP_PROFILE_SCOPE(s, "grid_backward", n);
-    const uint32_t threads = (uint32_t)next_multiple(n, 8) * (g.padded_width / 8);
-    const uint32_t blocks = div_round_up(threads, 256);
+    const dim3 blocks(div_round_up(n, 256), g.padded_width / 8, 1);
     GRID_DISPATCH(grid_backward_kernel, g, x, x_stride, n, dy, dy_layout, grad);
 }
 

@@ -680,3 +680,20 @@ extern "C" void ref_render_nerf(const RefRenderCfg* c, const RefNerfNetCfg* net,
         if (a > 0.2f) depth_out[idx] = ldepth;
     }
 }
+
+// ---- exports of the scalar helpers for the reference-pinning tests (tests/test_oracle_pins.py, tests/golden/) ----
+extern "C" float ref_advance_to_next_voxel(float t, float cone, const float* pos, const float* dir, uint32_t mip) {
+    V3 d = ld3(dir);
+    return advance_to_next_voxel(t, cone, ld3(pos), d, v3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z), mip);
+}
+extern "C" float ref_warp_dt(float dt) { return warp_dt(dt); }
+extern "C" float ref_unwarp_dt(float dt) { return unwarp_dt(dt); }
+extern "C" float ref_network_to_rgb(float v, int act) { return network_to_rgb(v, act); }
+extern "C" float ref_network_to_rgb_derivative(float v, int act) { return network_to_rgb_derivative(v, act); }
+extern "C" float ref_network_to_density(float v, int act) { return network_to_density(v, act); }
+extern "C" float ref_network_to_density_derivative(float v, int act) { return network_to_density_derivative(v, act); }
+extern "C" void ref_loss_and_gradient(const float* target, const float* prediction, int loss_type, float* out) {
+    LG lg = loss_and_gradient(ld3(target), ld3(prediction), loss_type);
+    out[0] = lg.loss.x; out[1] = lg.loss.y; out[2] = lg.loss.z; out[3] = lg.grad.x; out[4] = lg.grad.y; out[5] = lg.grad.z;
+}
+extern "C" int ref_aabb_contains(const RefAabb* b, const float* p) { return aabb_contains(b, ld3(p)) ? 1 : 0; }

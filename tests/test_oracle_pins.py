@@ -1,0 +1,94 @@
+"""Pins the oracle's in-mount restatements against the reference's OWN code: tests/golden/reference_helpers.npz was produced
+by compiling include/neural-graphics-primitives/{random_val,bounding_box,common_device}.cuh and the helper functions of
+src/testbed_nerf.cu with g++ (oracle/ref_shim, tests/golden/make_golden.py).  Integer results must be identical; float
+results must be bit-identical too (both sides are IEEE evaluations of the same expressions) except where noted."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+G = np.load(os.path.join(os.path.dirname(__file__), "golden", "reference_helpers.npz"))
+
+
+@pytest.fixture(scope="module")
+def L(ref):
+    l = ref.lib()
+    f32, u32, i32, vp = C.c_float, C.c_uint32, C.c_int, C.c_void_p
+    for name, res, args in [("ref_advance_to_next_voxel", f32, [f32, f32, vp, vp, u32]), ("ref_warp_dt", f32, [f32]), ("ref_unwarp_dt", f32, [f32]),
+                            ("ref_network_to_rgb", f32, [f32, i32]), ("ref_network_to_rgb_derivative", f32, [f32, i32]),
+                            ("ref_network_to_density", f32, [f32, i32]), ("ref_network_to_density_derivative", f32, [f32, i32]),
+                            ("ref_mip_from_pos", u32, [vp, u32]), ("ref_mip_from_dt", u32, [f32, vp, u32]), ("ref_cascaded_grid_idx_at", u32, [vp, u32]),
+                            ("ref_density_grid_occupied_at", i32, [vp, vp, u32]), ("ref_aabb_contains", i32, [vp, vp])]:
+        getattr(l, name).restype = res; getattr(l, name).argtypes = args
+    return l
+
+
+def _same(a, b):
+    a = np.asarray(a); b = np.asarray(b)
+    return np.array_equal(a.view(np.uint32) if a.dtype == np.float32 else a, b.view(np.uint32) if b.dtype == np.float32 else b)
+
+
+def test_low_discrepancy_sequence(ref, L):
+    got = np.array([L.ref_ld_random_val(int(a), int(b)) for a, b in zip(G["ld_index"], G["ld_seed"])], np.float32)
+    assert _same(got, G["ld_val"])
+    v2 = np.zeros_like(G["ld_val_2d"])
+    for k in range(len(v2)):
+        L.ref_ld_random_val_2d(C.c_uint32(int(G["ld_index"][k])), C.c_uint32(int(G["ld_seed"][k])), ref.P(v2[k]))
+    assert _same(v2, G["ld_val_2d"])
+
+
+def test_colour_conversions(L):
+    x = G["colour_x"]
+    assert _same(np.array([L.ref_srgb_to_linear(float(a)) for a in x], np.float32), G["srgb_to_linear"])
+    assert _same(np.array([L.ref_linear_to_srgb(float(a)) for a in x], np.float32), G["linear_to_srgb"])
+
+
+@pytest.mark.parametrize("tag,cone", [("c0", 0.0), ("c256", 1.0 / 256.0)])
+def test_exponential_stepping(L, tag, cone):
+    t = G["step_t"]
+    n = np.array([L.ref_to_stepping_space(float(a), cone) for a in t], np.float32)
+    assert _same(n, G[f"to_stepping_{tag}"])
+    assert _same(np.array([L.ref_from_stepping_space(float(a), cone) for a in n], np.float32), G[f"from_stepping_{tag}"])
+    assert _same(np.array([L.ref_calc_dt(float(a), cone) for a in t], np.float32), G[f"calc_dt_{tag}"])
+    assert _same(np.array([L.ref_advance_n_steps(float(a), cone, 0.5) for a in t], np.float32), G[f"advance_half_{tag}"])
+
+
+def test_occupancy_lookups_and_voxel_skip(ref, L):
+    pos, d, tt = G["occ_pos"], G["occ_dir"], G["occ_t"]
+    bitfield = np.random.default_rng(int(G["bitfield_seed"][0])).integers(0, 256, 128 ** 3 * 8 // 8, dtype=np.uint16).astype(np.uint8)
+    for mc in (0, 3, 7):
+        assert np.array_equal(np.array([L.ref_mip_from_pos(ref.P(p), mc) for p in pos], np.uint32), G[f"mip_from_pos_{mc}"])
+        assert np.array_equal(np.array([L.ref_mip_from_dt(float(dt), ref.P(p), mc) for p, dt in zip(pos, G["calc_dt_c256"])], np.uint32), G[f"mip_from_dt_{mc}"])
+    mips = G["mip_from_pos_7"]
+    assert np.array_equal(np.array([L.ref_cascaded_grid_idx_at(ref.P(p), int(m)) for p, m in zip(pos, mips)], np.uint32), G["grid_idx"])
+    occ = np.array([L.ref_density_grid_occupied_at(ref.P(p), ref.P(bitfield), int(m)) for p, m in zip(pos, mips)], np.int32)
+    assert np.array_equal(occ != 0, G["occupied"] != 0) and 0.2 < (occ != 0).mean() < 0.8
+    for tag, cone in (("c0", 0.0), ("c256", 1.0 / 256.0)):
+        nv = np.array([L.ref_advance_to_next_voxel(float(a), cone, ref.P(p), ref.P(q), int(m)) for a, p, q, m in zip(tt, pos, d, mips)], np.float32)
+        assert _same(nv, G[f"next_voxel_{tag}"])
+
+
+def test_bounding_box(ref, L):
+    aabb = ref.make_aabb((0, 0, 0), (1, 1, 1))
+    out = np.zeros((len(G["aabb_o"]), 2), np.float32)
+    for k in range(len(out)):
+        L.ref_aabb_ray_intersect(C.byref(aabb), ref.P(G["aabb_o"][k]), ref.P(G["occ_dir"][k]), ref.P(out[k]))
+    assert _same(out, G["aabb_isect"])
+    assert np.array_equal(np.array([L.ref_aabb_contains(C.byref(aabb), ref.P(p)) for p in G["occ_pos"]], np.int32) != 0, G["aabb_contains"] != 0)
+
+
+def test_dt_warp_activations_and_losses(ref, L):
+    dt = G["dt"]
+    w = np.array([L.ref_warp_dt(float(a)) for a in dt], np.float32)
+    assert _same(w, G["warp_dt"])
+    assert _same(np.array([L.ref_unwarp_dt(float(a)) for a in w], np.float32), G["unwarp_dt"])
+    for act in range(4):
+        for fn in ("network_to_rgb", "network_to_rgb_derivative", "network_to_density", "network_to_density_derivative"):
+            got = np.array([getattr(L, "ref_" + fn)(float(a), act) for a in G["act_x"]], np.float32)
+            assert _same(got, G[f"{fn}_{act}"]), (fn, act)
+    for lt in range(7):
+        lg = np.zeros_like(G[f"loss_{lt}"])
+        for k in range(len(lg)):
+            L.ref_loss_and_gradient(ref.P(G["loss_target"][k]), ref.P(G["loss_pred"][k]), lt, ref.P(lg[k]))
+        assert _same(lg, G[f"loss_{lt}"]), lt
