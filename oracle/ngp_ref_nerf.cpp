@@ -408,6 +408,12 @@ static inline void random_image_pos_training(RefPcg32* rng, const int32_t* res, 
     }
 }
 
+// Data-parallel sharding (no reference counterpart): rank r of G draws the global ray indices
+// [r*R, (r+1)*R) of a G*R-ray step — image choice, RNG stream and loss normalisation use the GLOBAL index / count.
+// (0, 0) = single process.  Mirrors ngp_testbed_set_shard of the CUDA library.
+static uint32_t g_ray_offset = 0, g_n_rays_global = 0;
+extern "C" void ref_set_shard(uint32_t ray_offset, uint32_t n_rays_global) { g_ray_offset = ray_offset; g_n_rays_global = n_rays_global; }
+
 extern "C" void ref_generate_training_samples(uint32_t n_rays, const RefAabb* aabb, uint32_t max_samples, uint32_t n_rays_total,
                                               uint64_t seed, uint64_t skip, uint32_t n_images, const RefImage* images,
                                               const uint8_t* bf, uint32_t max_mip, int snap, float cone_angle_constant,
@@ -415,10 +421,12 @@ extern "C" void ref_generate_training_samples(uint32_t n_rays, const RefAabb* aa
     (void)n_rays_total;
     RefPcg32 base; ref_pcg32_seed(&base, seed, 1); ref_pcg32_advance(&base, (int64_t)skip);
     uint32_t ray_counter = 0, numsteps_counter = 0;
+    const uint32_t n_global = g_n_rays_global ? g_n_rays_global : n_rays;
     for (uint32_t i = 0; i < n_rays; ++i) {
-        uint32_t img = image_idx(i, n_rays, n_images);
+        const uint32_t ig = g_ray_offset + i;
+        uint32_t img = image_idx(ig, n_global, n_images);
         const RefImage* m = &images[img];
-        RefPcg32 rng = base; ref_pcg32_advance(&rng, (int64_t)((uint64_t)i * REF_N_MAX_RANDOM_SAMPLES_PER_RAY));
+        RefPcg32 rng = base; ref_pcg32_advance(&rng, (int64_t)((uint64_t)ig * REF_N_MAX_RANDOM_SAMPLES_PER_RAY));
         float uv[2]; random_image_pos_training(&rng, m->res, snap, uv);
         float texel[4]; read_rgba(m, uv, texel);
         if (texel[0] < 0.0f) continue;                      // masked-away pixel (:1430-1435)
@@ -497,6 +505,7 @@ extern "C" void ref_compute_loss(uint32_t n_rays, const RefAabb* aabb, uint32_t 
                                  uint32_t n_images, const RefImage* images, const uint16_t* net_out,
                                  const uint32_t* ray_indices, const float* rays, const float* coords, RefLossOut* out) {
     (void)n_rays_total;
+    const uint32_t n_global = g_n_rays_global ? g_n_rays_global : n_rays;
     RefPcg32 base; ref_pcg32_seed(&base, seed, 1); ref_pcg32_advance(&base, (int64_t)skip);
     uint32_t compacted_counter = 0;
     for (uint32_t i = 0; i < rays_counter; ++i) {
@@ -518,9 +527,9 @@ extern "C" void ref_compute_loss(uint32_t n_rays, const RefAabb* aabb, uint32_t 
             T *= (1.f - alpha);
         }
         // RNG replay (:1757-1780)
-        uint32_t ray_idx = ray_indices[i];
+        uint32_t ray_idx = g_ray_offset + ray_indices[i];
         RefPcg32 rng = base; ref_pcg32_advance(&rng, (int64_t)((uint64_t)ray_idx * REF_N_MAX_RANDOM_SAMPLES_PER_RAY));
-        uint32_t img = image_idx(ray_idx, n_rays, n_images);
+        uint32_t img = image_idx(ray_idx, n_global, n_images);
         const RefImage* m = &images[img];
         float uv[2]; random_image_pos_training(&rng, m->res, cfg->snap_to_pixel_centers, uv);
         ref_pcg32_advance(&rng, 1);   // motionblur_time
@@ -549,9 +558,9 @@ extern "C" void ref_compute_loss(uint32_t n_rays, const RefAabb* aabb, uint32_t 
 
         LG lg = loss_and_gradient(target, rgb_ray, cfg->loss_type);
         float mean_loss = (lg.loss.x + lg.loss.y + lg.loss.z) / 3.0f;
-        if (out->loss) out->loss[i] = mean_loss / (float)n_rays;
+        if (out->loss) out->loss[i] = mean_loss / (float)n_global;
 
-        float loss_scale = cfg->loss_scale / (float)n_rays;
+        float loss_scale = cfg->loss_scale / (float)n_global;
         const float output_l2_reg = cfg->rgb_activation == REF_ACT_EXPONENTIAL ? 1e-4f : 0.0f;
         const float output_l1_reg_density = cfg->mean_density < REF_NERF_MIN_OPTICAL_THICKNESS ? 1e-4f : 0.0f;
 
