@@ -638,6 +638,10 @@ void nerf_generate_training_samples(cudaStream_t s, uint32_t n_rays, Aabb aabb, 
 //   scan  : exclusive prefix of the compacted step counts (replaces atomicAdd(numsteps_counter_compacted, ...))
 //   pass 2: loss + analytic dL/d(rgb,sigma) per kept sample, coordinates copied to the compacted batch
 // =================================================================================================================
+NGP_D void copy_enc_row(const __half* __restrict__ src, __half* __restrict__ dst, uint32_t src_row, uint32_t dst_row, uint32_t width) {
+    for (uint32_t c = 0; c < width / 8; ++c)
+        *reinterpret_cast<uint4*>(dst + blk8_chunk_offset(dst_row, c, width)) = __ldg(reinterpret_cast<const uint4*>(src + blk8_chunk_offset(src_row, c, width)));
+}
 struct LG { V3 loss, grad; };
 NGP_D LG loss_and_gradient(V3 target, V3 pred, int type) {   // :207-283,1340-1355
     const float d[3] = {pred.x - target.x, pred.y - target.y, pred.z - target.z}, p[3] = {pred.x, pred.y, pred.z}, tg[3] = {target.x, target.y, target.z};
@@ -749,6 +753,7 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_backward_kernel(uint32_t n_ra
         float c[7];
 #pragma unroll
         for (int k = 0; k < 7; ++k) { c[k] = __ldg(cin + (size_t)j * 7 + k); cout[(size_t)j * 7 + k] = c[k]; }
+        if (lb.enc_out) copy_enc_row(lb.enc_in, lb.enc_out, base + j, cbase + j, lb.enc_width);
         const V3 pos = unwarp_position(v3(c[0], c[1], c[2]), aabb);
         const float depth = length3(pos - ray_o);
         const float dt = unwarp_dt(c[3]);
@@ -885,6 +890,7 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_backward_group_kernel(uint32_
             float c[7];
 #pragma unroll
             for (int k = 0; k < 7; ++k) { c[k] = __ldg(cin + (size_t)j * 7 + k); cout[(size_t)j * 7 + k] = c[k]; }
+            if (lb.enc_out) copy_enc_row(lb.enc_in, lb.enc_out, base + j, cbase + j, lb.enc_width);
             const V3 pos = unwarp_position(v3(c[0], c[1], c[2]), aabb);
             depth = length3(pos - ray_o);
             dt = unwarp_dt(c[3]);
@@ -940,7 +946,8 @@ void nerf_compute_loss(cudaStream_t s, uint32_t n_rays, Aabb aabb, uint32_t n_ra
 
 // fill_rollover_and_rescale<T> / fill_rollover<T> (tcnn, recalled; testbed_nerf.cu:4061-4069): entries [n_input, n_target) are
 // cyclic copies of [0, n_input); the gradient copies are multiplied by n_input/n_target.
-__global__ void fill_rollover_kernel(uint32_t n_target, const uint32_t* __restrict__ n_input_ptr, __half* __restrict__ dloss, float* __restrict__ coords) {
+__global__ void fill_rollover_kernel(uint32_t n_target, const uint32_t* __restrict__ n_input_ptr, __half* __restrict__ dloss, float* __restrict__ coords,
+                                     __half* __restrict__ enc, uint32_t enc_width) {
     const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x;
     const uint32_t n_input = min(*n_input_ptr, n_target);
     if (i < n_input || i >= n_target || n_input == 0) return;
@@ -953,10 +960,11 @@ __global__ void fill_rollover_kernel(uint32_t n_target, const uint32_t* __restri
     *reinterpret_cast<uint2*>(dloss + (size_t)i * 4) = *reinterpret_cast<uint2*>(o);
 #pragma unroll
     for (int k = 0; k < 7; ++k) coords[(size_t)i * 7 + k] = coords[(size_t)src * 7 + k];
+    if (enc) copy_enc_row(enc, enc, src, i, enc_width);
 }
-void nerf_fill_rollover(cudaStream_t s, uint32_t n_target, const uint32_t* n_input_dev, __half* dloss, float* coords) {
+void nerf_fill_rollover(cudaStream_t s, uint32_t n_target, const uint32_t* n_input_dev, __half* dloss, float* coords, __half* enc, uint32_t enc_width) {
     NGP_PROFILE_SCOPE(s, "fill_rollover", n_target);
-    fill_rollover_kernel<<<div_round_up(n_target, 256), 256, 0, s>>>(n_target, n_input_dev, dloss, coords);
+    fill_rollover_kernel<<<div_round_up(n_target, 256), 256, 0, s>>>(n_target, n_input_dev, dloss, coords, enc, enc_width);
     NGP_POST_LAUNCH();
 }
 

@@ -53,12 +53,15 @@ struct LossBuffers {
     float* loss;                    // [n_rays]
     float* ray_scratch;             // [n_rays][8]: rgb_ray(3), target(3), spare
     uint32_t* compacted_numsteps;   // [n_rays] pass-1 compacted step counts
+    // optional: encoder outputs of the un-compacted samples (blk8, enc_width columns) are carried along with the samples that
+    // survive compaction, so the training forward pass does not gather the hash grid a second time for the same points
+    const __half* enc_in; __half* enc_out; uint32_t enc_width;
 };
 void nerf_compute_loss(cudaStream_t s, uint32_t n_rays, Aabb aabb, uint32_t n_rays_total, Pcg32 rng, uint32_t max_samples_compacted,
                        const LossConfig& cfg, uint32_t n_images, const ImageMeta* metas, const float* mean_density_dev,
                        uint32_t ray_offset, uint32_t n_rays_global, const SamplerBuffers& sb, const LossBuffers& lb);
 // fill_rollover_and_rescale + fill_rollover (tcnn; testbed_nerf.cu:4061-4069) on dL [n_target][4] fp16 and coords [n_target][7]
-void nerf_fill_rollover(cudaStream_t s, uint32_t n_target, const uint32_t* n_input_dev, __half* dloss, float* coords);
+void nerf_fill_rollover(cudaStream_t s, uint32_t n_target, const uint32_t* n_input_dev, __half* dloss, float* coords, __half* enc = nullptr, uint32_t enc_width = 0);
 // sum of loss[0..n) -> *out_dev (deterministic)
 void reduce_sum_f32(cudaStream_t s, const float* in, uint32_t n, float* out_dev, float* partials /* [1024] */);
 

@@ -112,6 +112,17 @@ void NerfNetwork::forward_backward(cudaStream_t s, const __half* params, const f
     grid_backward(s, grid, coords, 7, n, denc, LAYOUT_BLK8, grads + off_grid);
 }
 
+void NerfNetwork::forward_backward_encoded(cudaStream_t s, const __half* params, const float* coords, uint32_t n, const __half* dL_dout, __half* grads) {
+    const __half* enc = enc_train_buf.as<__half>();
+    __half* denc = denc_buf.get<__half>((size_t)n * dims.pos_width);
+    float* wg = wgrad_buf.get<float>(n_matrix_params);
+    NGP_CUDA_CHECK(cudaMemsetAsync(wg, 0, n_matrix_params * sizeof(float), s));
+    NGP_CUDA_CHECK(cudaMemsetAsync(grads + off_grid, 0, grid.n_params * sizeof(__half), s));
+    nerf_mlp_backward(s, dims, params + off_density, params + off_rgb, enc, coords, n, dL_dout, denc, wg);
+    cast_f32_to_half(s, wg, grads, n_matrix_params);
+    grid_backward(s, grid, coords, 7, n, denc, LAYOUT_BLK8, grads + off_grid);
+}
+
 // ---------------------------------------------------------------------------------------------------------------
 EncodedMlp::EncodedMlp(const Json& cfg, uint32_t n_pos_dims, uint32_t n_output_dims) {
     NGP_CHECK(cfg.contains("encoding") && cfg.contains("network"), "network config needs 'encoding' and 'network'");

@@ -34,7 +34,7 @@ void mlp_init_host(uint32_t in_w, uint32_t n_hidden, Pcg32& rng, float* params);
 struct NerfNetwork {
     GridLayout grid; NerfNetDims dims;
     uint64_t off_density = 0, off_rgb = 0, off_grid = 0, n_params = 0, n_matrix_params = 0;
-    DeviceBuffer enc_buf, denc_buf, wgrad_buf;
+    DeviceBuffer enc_buf, denc_buf, wgrad_buf, enc_train_buf;
 
     // config = the reference's network JSON ("encoding", "network", "dir_encoding", "rgb_network")
     explicit NerfNetwork(const Json& config);
@@ -45,6 +45,10 @@ struct NerfNetwork {
     void density(cudaStream_t s, const __half* params, const float* pos, uint32_t pos_stride, uint32_t n, __half* out);
     // forward(recompute)+backward; grads: param-shaped fp16, OVERWRITTEN (EGradientMode::Overwrite, testbed_nerf.cu:4078)
     void forward_backward(cudaStream_t s, const __half* params, const float* coords, uint32_t n, const __half* dL_dout, __half* grads);
+    // same, with the encoder outputs of the n samples already known (blk8 rows in enc_train_buf, carried over from inference())
+    void forward_backward_encoded(cudaStream_t s, const __half* params, const float* coords, uint32_t n, const __half* dL_dout, __half* grads);
+    const __half* last_inference_encoding() const { return enc_buf.as<__half>(); }
+    __half* training_encoding(uint32_t n) { return enc_train_buf.get<__half>((size_t)n * dims.pos_width); }
 };
 
 struct EncodedMlp {

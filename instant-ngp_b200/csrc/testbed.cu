@@ -237,6 +237,7 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
     lb.coords_compacted = m_coords_compacted.get<float>((size_t)target * 7); lb.loss = m_loss.get<float>(max_rays);
     lb.ray_scratch = m_ray_scratch.get<float>((size_t)max_rays * 8); lb.compacted_numsteps = m_compacted_numsteps.get<uint32_t>(max_rays);
     m_loss_sum.get<float>(4);
+    lb.enc_width = m_nerf_net->dims.pos_width; lb.enc_out = m_nerf_net->training_encoding(target);
 
     uint32_t max_inference;
     if (m_measured_before == 0) { m_measured_before = max_inference = max_samples; }
@@ -259,10 +260,11 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
     lc.random_bg_color = random_bg_color; lc.linear_colors = linear_colors; lc.snap_to_pixel_centers = snap_to_pixel_centers;
     memcpy(lc.background_color, background_color, sizeof(lc.background_color));
     lc.loss_scale = LOSS_SCALE; lc.near_distance = near_distance;
+    lb.enc_in = m_nerf_net->last_inference_encoding();   // written by inference() just above
     nerf_compute_loss(s, R, aabb, n_rays_total, m_rng, target, lc, m_n_images, m_metas.as<ImageMeta>(), m_mean.as<float>(), ray_offset, n_rays_global, sb, lb);
-    nerf_fill_rollover(s, target, &sb.counters[2], lb.dloss_doutput, lb.coords_compacted);   // :4061-4069
+    nerf_fill_rollover(s, target, &sb.counters[2], lb.dloss_doutput, lb.coords_compacted, lb.enc_out, lb.enc_width);   // :4061-4069
     // forward(compacted) + backward(EGradientMode::Overwrite) (:4077-4078)
-    m_nerf_net->forward_backward(s, m_trainer->params, lb.coords_compacted, target, lb.dloss_doutput, m_trainer->grads);
+    m_nerf_net->forward_backward_encoded(s, m_trainer->params, lb.coords_compacted, target, lb.dloss_doutput, m_trainer->grads);
     m_rng.advance();   // :4127
 }
 
