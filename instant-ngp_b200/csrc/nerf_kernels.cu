@@ -4,6 +4,7 @@
 // atomicAdd (nondeterministic sample order); here block-level warp-shuffle scans + a one-block scan of
 // the block totals give the same set of samples in ray order, so results are reproducible and comparable per slot.
 #include "nerf_kernels.h"
+#include <cstdlib>
 
 namespace ngp {
 
@@ -796,13 +797,19 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_forward_group_kernel(uint32_t
         float T = 1.f; const float epsilon = 1e-4f;
         V3 rgb_ray = v3(0, 0, 0);
         bool stop = false;
+        // software pipeline: the raw loads of chunk c+1 are in flight while the recurrence of chunk c is replayed
+        uint2 raw_next = make_uint2(0u, 0u); float dtw_next = 0.f;
+        if (lane < numsteps) { raw_next = __ldg(reinterpret_cast<const uint2*>(no + (size_t)lane * 4)); dtw_next = __ldg(cin + (size_t)lane * 7 + 3); }
         for (uint32_t c0 = 0; c0 < numsteps && !stop; c0 += G) {
             const uint32_t idx = c0 + lane;
+            const uint2 raw = raw_next; const float dtw = dtw_next;
+            if (idx + G < numsteps) { raw_next = __ldg(reinterpret_cast<const uint2*>(no + (size_t)(idx + G) * 4)); dtw_next = __ldg(cin + (size_t)(idx + G) * 7 + 3); }
             float alpha = 0.f; V3 rgb = v3(0, 0, 0);
             if (idx < numsteps) {
-                float o[4]; load_out4(no + (size_t)idx * 4, o);
+                const __half* h = reinterpret_cast<const __half*>(&raw);
+                const float o[4] = {__half2float(h[0]), __half2float(h[1]), __half2float(h[2]), __half2float(h[3])};
                 rgb = v3(network_to_rgb(o[0], cfg.rgb_activation), network_to_rgb(o[1], cfg.rgb_activation), network_to_rgb(o[2], cfg.rgb_activation));
-                const float dt = unwarp_dt(__ldg(cin + (size_t)idx * 7 + 3));
+                const float dt = unwarp_dt(dtw);
                 const float density = network_to_density(o[3], cfg.density_activation);
                 alpha = 1.f - expf(-density * dt);
             }
@@ -882,19 +889,32 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_backward_group_kernel(uint32_
     V3 rgb_ray2 = v3(0, 0, 0); float T = 1.f;
     __half* gout = lb.dloss_doutput + (size_t)cbase * 4;
     float* cout = lb.coords_compacted + (size_t)cbase * 7;
+    float c_next[7] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}; uint2 raw_next = make_uint2(0u, 0u);
+    if (lane < cn) {
+#pragma unroll
+        for (int k = 0; k < 7; ++k) c_next[k] = __ldg(cin + (size_t)lane * 7 + k);
+        raw_next = __ldg(reinterpret_cast<const uint2*>(no + (size_t)lane * 4));
+    }
     for (uint32_t c0 = 0; c0 < cn; c0 += G) {
         const uint32_t j = c0 + lane;
         const bool valid = j < cn;
+        float c[7]; const uint2 raw = raw_next;
+#pragma unroll
+        for (int k = 0; k < 7; ++k) c[k] = c_next[k];
+        if (j + G < cn) {   // next chunk's loads fly while this chunk's recurrence is replayed
+#pragma unroll
+            for (int k = 0; k < 7; ++k) c_next[k] = __ldg(cin + (size_t)(j + G) * 7 + k);
+            raw_next = __ldg(reinterpret_cast<const uint2*>(no + (size_t)(j + G) * 4));
+        }
         float o[4] = {0.f, 0.f, 0.f, 0.f}; V3 rgb = v3(0, 0, 0); float alpha = 0.f, dt = 0.f, depth = 0.f;
         if (valid) {
-            float c[7];
 #pragma unroll
-            for (int k = 0; k < 7; ++k) { c[k] = __ldg(cin + (size_t)j * 7 + k); cout[(size_t)j * 7 + k] = c[k]; }
+            for (int k = 0; k < 7; ++k) cout[(size_t)j * 7 + k] = c[k];
             if (lb.enc_out) copy_enc_row(lb.enc_in, lb.enc_out, base + j, cbase + j, lb.enc_width);
             const V3 pos = unwarp_position(v3(c[0], c[1], c[2]), aabb);
             depth = length3(pos - ray_o);
             dt = unwarp_dt(c[3]);
-            load_out4(no + (size_t)j * 4, o);
+            { const __half* h = reinterpret_cast<const __half*>(&raw); o[0] = __half2float(h[0]); o[1] = __half2float(h[1]); o[2] = __half2float(h[2]); o[3] = __half2float(h[3]); }
             rgb = v3(network_to_rgb(o[0], cfg.rgb_activation), network_to_rgb(o[1], cfg.rgb_activation), network_to_rgb(o[2], cfg.rgb_activation));
             const float density = network_to_density(o[3], cfg.density_activation);
             alpha = 1.f - expf(-density * dt);
@@ -930,7 +950,9 @@ void nerf_compute_loss(cudaStream_t s, uint32_t n_rays, Aabb aabb, uint32_t n_ra
                        const SamplerBuffers& sb, const LossBuffers& lb) {
     (void)n_rays_total;
     NGP_PROFILE_SCOPE(s, "loss", n_rays);
-    const uint32_t G = sb.lanes_per_ray == 1 ? 1u : (n_rays <= 2048 ? 32u : 8u);
+    // a whole warp per ray unless rays are plentiful: the slowest (longest) ray bounds the kernel, and 32 lanes cut its chunk count 4x
+    uint32_t G = sb.lanes_per_ray == 1 ? 1u : (n_rays <= 65536 ? 32u : 8u);
+    if (const char* e = getenv("NGP_LOSS_LANES")) G = (uint32_t)atoi(e);
     const uint32_t blocks = div_round_up(n_rays, SCAN_BLOCK / G);
     if (G == 32) loss_forward_group_kernel<32><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, rng, cfg, n_images, metas, ray_offset, n_rays_global, sb, lb);
     else if (G == 8) loss_forward_group_kernel<8><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, rng, cfg, n_images, metas, ray_offset, n_rays_global, sb, lb);
