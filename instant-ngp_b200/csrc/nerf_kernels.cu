@@ -459,35 +459,75 @@ __global__ void __launch_bounds__(SCAN_BLOCK) sampler_write_kernel(uint32_t n_ra
 // current run (occupied / empty) continues, lane k keeping candidate k, then test all G cells with one ballot.  The
 // candidates up to the first misprediction are exactly the serial walk's; the group restarts from there in the other
 // mode.  Every float operation is the serial one, so positions, sample counts and coordinates are bit-identical.
-template <uint32_t G, bool WRITE, bool FLAT>
+// ---- G lanes per ray, K candidates per lane ------------------------------------------------------------------------
+// A round speculates C = G*K candidates: the lanes of a group advance the (serial, bit-exact) t chain C steps in lock
+// step, under the current hypothesis (step mode: "every candidate is an occupied sample", skip mode: "every candidate is
+// empty and the walk jumps to the next voxel"); lane g keeps t of candidates g, G+g, ..; then each lane evaluates its own
+// K candidates (position, aabb test, dt, occupancy byte: K independent loads) and ballots tell where the hypothesis first
+// fails.  The chain loop carries no aabb test and no capture beyond one select: candidates past the exit are computed and
+// ignored.  Warp instructions per ray scale with 1/rays-per-warp = G/32 at a fixed C, which is why K > 1 pays.
+template <bool FLAT, bool STEP>
+NGP_D float chain_next(float t, const RayConst& rc, float cone, uint32_t max_mip) {
+    if (FLAT && STEP) { const float n = div_by_stepsize(t); return t + ((n + 1.0f) * MIN_CONE_STEPSIZE() - t); }
+    const V3 pos = ray_at(rc.o, rc.d, t);
+    float dt, n; uint32_t mip;
+    candidate_dt_mip<FLAT>(t, pos, cone, max_mip, dt, mip, n);
+    return STEP ? t + dt : candidate_skip<FLAT>(t, n, pos, rc, cone, mip);
+}
+template <uint32_t G, uint32_t K, bool FLAT, bool STEP>
+NGP_D float chain_round(float t, float* my_t, uint32_t lane, const RayConst& rc, float cone, uint32_t max_mip) {
+#pragma unroll
+    for (uint32_t k = 0; k < K; ++k) {
+#pragma unroll (G < 8 ? G : 8)
+        for (uint32_t g = 0; g < G; ++g) {
+            if (g == lane) my_t[k] = t;
+            t = chain_next<FLAT, STEP>(t, rc, cone, max_mip);
+        }
+    }
+    return t;
+}
+template <uint32_t G, bool WRITE, bool FLAT, uint32_t K = 1>
 NGP_D uint32_t march_training_ray_group(V3 o, V3 d, float startt, float cone, const Aabb& aabb, const uint8_t* __restrict__ bitfield, uint32_t max_mip,
                                         uint32_t limit, float* __restrict__ coords, uint32_t lane, uint32_t gshift, uint32_t gmask, SampleLog* log = nullptr) {
-    constexpr uint32_t FULL = G == 32 ? 0xffffffffu : ((1u << G) - 1u);
+    constexpr uint32_t C = G * K;
+    static_assert(C <= 32, "at most 32 candidates per round");
+    constexpr uint32_t FULL_G = G == 32 ? 0xffffffffu : ((1u << G) - 1u);
+    constexpr uint32_t FULL_C = C == 32 ? 0xffffffffu : ((1u << C) - 1u);
     if (limit == 0) return 0;
     const RayConst rc = make_ray_const(o, d);
     const V3 wd = warp_direction(d);
     uint32_t j = 0; float t_base = startt; bool step_mode = false;
     while (true) {
-        float t = t_base, my_t = 0.f, my_dt = 0.f, my_n = 0.f; V3 my_pos = v3(0.f, 0.f, 0.f); uint32_t my_mip = 0, n_valid = G;
-#pragma unroll 1
-        for (uint32_t it = 0; it < G; ++it) {
-            const V3 pos = ray_at(o, d, t);
-            if (!aabb_contains(aabb, pos)) { n_valid = it; break; }
-            float dt, n; uint32_t mip;
-            candidate_dt_mip<FLAT>(t, pos, cone, max_mip, dt, mip, n);
-            if (it == lane) { my_t = t; my_dt = dt; my_n = n; my_pos = pos; my_mip = mip; }
-            t = step_mode ? t + dt : candidate_skip<FLAT>(t, n, pos, rc, cone, mip);
+        float my_t[K], my_dt[K];
+        const float t_end = step_mode ? chain_round<G, K, FLAT, true>(t_base, my_t, lane, rc, cone, max_mip)
+                                      : chain_round<G, K, FLAT, false>(t_base, my_t, lane, rc, cone, max_mip);
+        uint32_t in_mask = 0, occ_mask = 0;
+#pragma unroll
+        for (uint32_t k = 0; k < K; ++k) {
+            const V3 pos = ray_at(o, d, my_t[k]);
+            const bool inside = aabb_contains(aabb, pos);
+            float n; uint32_t mip;
+            candidate_dt_mip<FLAT>(my_t[k], pos, cone, max_mip, my_dt[k], mip, n);
+            const bool occ = inside && density_grid_occupied_at(pos, bitfield, mip);
+            in_mask |= ((__ballot_sync(gmask, inside) >> gshift) & FULL_G) << (k * G);
+            occ_mask |= ((__ballot_sync(gmask, occ) >> gshift) & FULL_G) << (k * G);
         }
-        const bool occ = lane < n_valid && density_grid_occupied_at(my_pos, bitfield, my_mip);
-        const uint32_t occ_mask = (__ballot_sync(gmask, occ) >> gshift) & FULL;
+        const uint32_t out = ~in_mask & FULL_C;
+        const uint32_t n_valid = out ? (uint32_t)__ffs((int)out) - 1u : C;    // first candidate outside the aabb ends the walk
+        occ_mask &= n_valid == 32 ? 0xffffffffu : ((1u << n_valid) - 1u);
         if (step_mode) {
-            const uint32_t bad = ~occ_mask & FULL;
-            const uint32_t f = bad ? (uint32_t)__ffs((int)bad) - 1u : G;     // first candidate that is not an occupied sample
+            const uint32_t bad = ~occ_mask & FULL_C;
+            const uint32_t f = bad ? (uint32_t)__ffs((int)bad) - 1u : C;       // first candidate that is not an occupied sample
             const uint32_t n_emit = min(f, limit - j);
-            if (WRITE && lane < n_emit) {
-                float* c = coords + (size_t)(j + lane) * 7;
-                const V3 wp = warp_position(my_pos, aabb);
-                c[0] = wp.x; c[1] = wp.y; c[2] = wp.z; c[3] = warp_dt(my_dt); c[4] = wd.x; c[5] = wd.y; c[6] = wd.z;
+            if (WRITE) {
+#pragma unroll
+                for (uint32_t k = 0; k < K; ++k) {
+                    if (k * G + lane < n_emit) {
+                        float* c = coords + (size_t)(j + k * G + lane) * 7;
+                        const V3 wp = warp_position(ray_at(o, d, my_t[k]), aabb);
+                        c[0] = wp.x; c[1] = wp.y; c[2] = wp.z; c[3] = warp_dt(my_dt[k]); c[4] = wd.x; c[5] = wd.y; c[6] = wd.z;
+                    }
+                }
             }
             if (!WRITE && n_emit) {
                 if (j + n_emit > log->cap && log->slot == NO_SLOT) {   // first sample beyond the window: take a pool slot (group-uniform)
@@ -495,26 +535,38 @@ NGP_D uint32_t march_training_ray_group(V3 o, V3 d, float startt, float cone, co
                     if (lane == 0) sl = atomicAdd(log->pool_counter, 1u);
                     log->slot = __shfl_sync(gmask, sl, gshift);
                 }
-                float2* dst = lane < n_emit ? log->at(j + lane) : nullptr;
-                if (dst) *dst = make_float2(my_t, my_dt);
+#pragma unroll
+                for (uint32_t k = 0; k < K; ++k) {
+                    float2* dst = k * G + lane < n_emit ? log->at(j + k * G + lane) : nullptr;
+                    if (dst) *dst = make_float2(my_t[k], my_dt[k]);
+                }
             }
             j += n_emit;
             if (j >= limit) break;
-            if (f == G) { t_base = t; continue; }
-            if (f >= n_valid) break;                                         // candidate f left the aabb: end of the walk
-            const float my_skip = candidate_skip<FLAT>(my_t, my_n, my_pos, rc, cone, my_mip);
-            t_base = __shfl_sync(gmask, my_skip, gshift + f);
+            if (f == C) { t_base = t_end; continue; }
+            if (f >= n_valid) break;                                           // candidate f left the aabb: end of the walk
+            float tf = my_t[0];
+#pragma unroll
+            for (uint32_t k = 1; k < K; ++k) if (k == f / G) tf = my_t[k];
+            const float my_skip = chain_next<FLAT, false>(tf, rc, cone, max_mip);
+            t_base = __shfl_sync(gmask, my_skip, gshift + f % G);
             step_mode = false;
         } else {
-            if (occ_mask) { t_base = __shfl_sync(gmask, my_t, gshift + (uint32_t)__ffs((int)occ_mask) - 1u); step_mode = true; continue; }
-            if (n_valid < G) break;
-            t_base = t;
+            if (occ_mask) {
+                const uint32_t f = (uint32_t)__ffs((int)occ_mask) - 1u;
+                float tf = my_t[0];
+#pragma unroll
+                for (uint32_t k = 1; k < K; ++k) if (k == f / G) tf = my_t[k];
+                t_base = __shfl_sync(gmask, tf, gshift + f % G); step_mode = true; continue;
+            }
+            if (n_valid < C) break;
+            t_base = t_end;
         }
     }
     return j;
 }
 
-template <uint32_t G, bool FLAT>
+template <uint32_t G, bool FLAT, uint32_t K>
 __global__ void __launch_bounds__(SCAN_BLOCK) sampler_count_group_kernel(uint32_t n_rays, Aabb aabb, Pcg32 rng, uint32_t n_images, const ImageMeta* __restrict__ metas,
                                                                          const uint8_t* __restrict__ bitfield, uint32_t max_mip, bool snap, float cone_angle_constant,
                                                                          uint32_t ray_offset, uint32_t n_rays_global, SamplerBuffers b) {
@@ -540,7 +592,7 @@ __global__ void __launch_bounds__(SCAN_BLOCK) sampler_count_group_kernel(uint32_
             tmin = fmaxf(tmin, 0.0f);
             const float startt = advance_n_steps(tmin, cone, rng.next_float());
             SampleLog log{b.sample_scratch + (size_t)i * b.scratch_per_ray, b.scratch_per_ray, b.sample_pool, b.pool_slots, &b.counters[3], NO_SLOT};
-            numsteps = march_training_ray_group<G, false, FLAT>(o, d, startt, cone, aabb, bitfield, max_mip, NERF_STEPS, nullptr, lane, gshift, gmask, &log);
+            numsteps = march_training_ray_group<G, false, FLAT, K>(o, d, startt, cone, aabb, bitfield, max_mip, NERF_STEPS, nullptr, lane, gshift, gmask, &log);
             if (lane == 0) b.overflow_slot[i] = log.slot;
             if (lane == 0) {
                 float* rt = b.ray_tmp + (size_t)i * 8;
@@ -608,26 +660,30 @@ void nerf_generate_training_samples(cudaStream_t s, uint32_t n_rays, Aabb aabb, 
     (void)n_rays_total;
     NGP_PROFILE_SCOPE(s, "sampler", n_rays);
     const uint32_t G = b.lanes_per_ray ? b.lanes_per_ray : nerf_sampler_lanes_per_ray(n_rays);
-    NGP_CHECK(G == 1 || G == 4 || G == 8 || G == 32, "sampler_lanes_per_ray must be 0 (automatic), 1, 4, 8 or 32");
+    NGP_CHECK(G == 1 || G == 2 || G == 4 || G == 8 || G == 32, "sampler_lanes_per_ray must be 0 (automatic), 1, 2, 4, 8 or 32");
+    uint32_t K = G == 32 ? 1u : 8u / G;                         // 8 candidates per round (32 with a whole warp per ray)
+    if (const char* e = getenv("NGP_SAMPLER_K")) K = (uint32_t)atoi(e);
     const bool flat = cone_angle_constant <= 1e-5f && max_mip == 0;
     const uint32_t blocks = div_round_up(n_rays, SCAN_BLOCK / G);
-#define NGP_SAMPLER_COUNT(GG, FF) sampler_count_group_kernel<GG, FF><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, rng, n_images, metas, bitfield, max_mip, snap, cone_angle_constant, ray_offset, n_rays_global, b)
-#define NGP_SAMPLER_WRITE(GG, FF) sampler_write_group_kernel<GG, FF><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, max_samples, bitfield, max_mip, b)
-#define NGP_SAMPLER_DISPATCH(WHAT)                                                       \
-    do {                                                                                 \
-        if (G == 32) { if (flat) WHAT(32, true); else WHAT(32, false); }                 \
-        else if (G == 8) { if (flat) WHAT(8, true); else WHAT(8, false); }               \
-        else if (G == 4) { if (flat) WHAT(4, true); else WHAT(4, false); }               \
-    } while (0)
+#define NGP_SAMPLER_COUNT(GG, FF, KK) sampler_count_group_kernel<GG, FF, KK><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, rng, n_images, metas, bitfield, max_mip, snap, cone_angle_constant, ray_offset, n_rays_global, b)
+#define NGP_SAMPLER_COUNT_F(GG, KK) do { if (flat) NGP_SAMPLER_COUNT(GG, true, KK); else NGP_SAMPLER_COUNT(GG, false, KK); } while (0)
+#define NGP_SAMPLER_WRITE(GG) do { if (flat) sampler_write_group_kernel<GG, true><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, max_samples, bitfield, max_mip, b); \
+                                   else sampler_write_group_kernel<GG, false><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, max_samples, bitfield, max_mip, b); } while (0)
     if (G == 1) { if (flat) sampler_count_kernel<true><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, rng, n_images, metas, bitfield, max_mip, snap, cone_angle_constant, ray_offset, n_rays_global, b);
                   else sampler_count_kernel<false><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, rng, n_images, metas, bitfield, max_mip, snap, cone_angle_constant, ray_offset, n_rays_global, b); }
-    else NGP_SAMPLER_DISPATCH(NGP_SAMPLER_COUNT);
+    else if (G == 32) NGP_SAMPLER_COUNT_F(32, 1);
+    else if (G == 8) { if (K == 2) NGP_SAMPLER_COUNT_F(8, 2); else NGP_SAMPLER_COUNT_F(8, 1); }
+    else if (G == 4) { if (K == 1) NGP_SAMPLER_COUNT_F(4, 1); else if (K == 4) NGP_SAMPLER_COUNT_F(4, 4); else NGP_SAMPLER_COUNT_F(4, 2); }
+    else { if (K == 8) NGP_SAMPLER_COUNT_F(2, 8); else NGP_SAMPLER_COUNT_F(2, 4); }
     NGP_POST_LAUNCH();
     scan_block_totals_kernel<<<1, 1024, 0, s>>>(blocks, b.block_steps, b.block_rays, &b.counters[1], nullptr, false);
     NGP_POST_LAUNCH();
     if (G == 1) { if (flat) sampler_write_kernel<true><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, max_samples, bitfield, max_mip, b);
                   else sampler_write_kernel<false><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, max_samples, bitfield, max_mip, b); }
-    else NGP_SAMPLER_DISPATCH(NGP_SAMPLER_WRITE);
+    else if (G == 32) NGP_SAMPLER_WRITE(32);
+    else if (G == 8) NGP_SAMPLER_WRITE(8);
+    else if (G == 4) NGP_SAMPLER_WRITE(4);
+    else NGP_SAMPLER_WRITE(2);
     NGP_POST_LAUNCH();
 }
 

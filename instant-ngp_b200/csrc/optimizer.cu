@@ -6,17 +6,34 @@
 // One pass, pure HBM streaming: 2 B grad + 4+4+4+4 B (master, m, v, step) r/w + 2 B param (+ 4+2 B EMA) per entry.
 #include "ngp_internal.h"
 #include <cmath>
+#include <mutex>
+#include <vector>
 
 namespace ngp {
 
-// 4 consecutive parameters per thread (16-byte accesses on the fp32 arrays, 8-byte on the fp16 ones).  Bias correction
-// 1 - beta^t is -expm1f(t * ln(beta)) (per-entry t because untouched hash entries do not step); the reference's powf costs
-// ~200 instructions per parameter and made the pass instruction-bound.
-struct AdamConsts { float ln_beta1, ln_beta2, ema_old_debias, ema_new_debias; };
+// 4 consecutive parameters per thread (16-byte accesses on the fp32 arrays, 8-byte on the fp16 ones).  The pass has to stay
+// under the HBM time of its ~30 B/parameter, i.e. ~25 instructions per parameter, so nothing transcendental is evaluated
+// per entry: the bias correction sqrt(1 - beta2^t) / (1 - beta1^t) depends on the entry's own step count t only (untouched
+// hash entries do not step) and is read from a table indexed by t, built once per (beta1, beta2) with
+// -expm1f(t * ln(beta)) (no cancellation; the reference's per-entry powf costs ~200 instructions per parameter);
+// 1 / (sqrt(v) + eps) uses the hardware approximations (2 ulp), divisions by launch constants are multiplications
+// by their reciprocals.  All within 1e-6 relative of the reference arithmetic (tests/test_ops_gpu.py: rtol 1e-5).
+constexpr uint32_t BIAS_TABLE_N = 1u << 15;
+struct AdamConsts { float ln_beta1, ln_beta2, ema_old_debias, inv_ema_new_debias, inv_loss_scale; const float* bias; };
+
+__device__ __noinline__ float bias_correction(float tf, float ln_beta1, float ln_beta2) {
+    return sqrtf(-expm1f(tf * ln_beta2)) / (-expm1f(tf * ln_beta1));   // sqrt(1 - beta2^t) / (1 - beta1^t)
+}
+__global__ void bias_table_kernel(float ln_beta1, float ln_beta2, float* __restrict__ tab) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < BIAS_TABLE_N) tab[t] = t == 0 ? 0.0f : bias_correction((float)t, ln_beta1, ln_beta2);
+}
+__device__ __forceinline__ float approx_sqrt(float x) { float y; asm("sqrt.approx.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float approx_rcp(float x) { float y; asm("rcp.approx.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 
 __device__ __forceinline__ void adam_one(const AdamHyper& h, const AdamConsts& c, bool matrix, float g_raw, float& w, float& m, float& v, uint32_t& t,
                                          bool& stepped) {
-    float g = g_raw / h.loss_scale;
+    float g = g_raw * c.inv_loss_scale;
     const bool skip = matrix ? !h.optimize_matrix : (!h.optimize_non_matrix || g == 0.0f);
     stepped = !skip;
     if (skip) return;
@@ -24,9 +41,8 @@ __device__ __forceinline__ void adam_one(const AdamHyper& h, const AdamConsts& c
     m = h.beta1 * m + (1.0f - h.beta1) * g;
     v = h.beta2 * v + (1.0f - h.beta2) * (g * g);
     ++t;
-    const float tf = (float)t;
-    const float lr = h.learning_rate * sqrtf(-expm1f(tf * c.ln_beta2)) / (-expm1f(tf * c.ln_beta1));   // 1 - beta^t without cancellation
-    w = w - lr / (sqrtf(v) + h.epsilon) * m;
+    const float corr = t < BIAS_TABLE_N ? __ldg(c.bias + t) : bias_correction((float)t, c.ln_beta1, c.ln_beta2);
+    w = w - h.learning_rate * corr * approx_rcp(approx_sqrt(v) + h.epsilon) * m;
 }
 
 __global__ void __launch_bounds__(256) adam_kernel(const AdamHyper h, const AdamConsts c, uint64_t n, float* __restrict__ master, __half* __restrict__ params,
@@ -66,7 +82,7 @@ __global__ void __launch_bounds__(256) adam_kernel(const AdamHyper h, const Adam
             __half eh[4];
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-                e[k] = (e[k] * h.ema_decay * c.ema_old_debias + __half2float(wh[k]) * (1.0f - h.ema_decay)) / c.ema_new_debias;
+                e[k] = (e[k] * h.ema_decay * c.ema_old_debias + __half2float(wh[k]) * (1.0f - h.ema_decay)) * c.inv_ema_new_debias;
                 eh[k] = __float2half_rn(e[k]);
             }
             *reinterpret_cast<float4*>(ema + i0) = e4;
@@ -81,19 +97,36 @@ __global__ void __launch_bounds__(256) adam_kernel(const AdamHyper h, const Adam
         __half wh = params[i];
         if (stepped) { master[i] = w; m[i] = mm; v[i] = vv; steps[i] = t; wh = __float2half_rn(w); params[i] = wh; }
         if (ema) {
-            const float f = (ema[i] * h.ema_decay * c.ema_old_debias + __half2float(wh) * (1.0f - h.ema_decay)) / c.ema_new_debias;
+            const float f = (ema[i] * h.ema_decay * c.ema_old_debias + __half2float(wh) * (1.0f - h.ema_decay)) * c.inv_ema_new_debias;
             ema[i] = f; ema_half[i] = __float2half_rn(f);
         }
     }
+}
+
+// one table per (device, beta1, beta2), built on first use and kept for the life of the process
+static const float* bias_table(cudaStream_t s, float ln_beta1, float ln_beta2) {
+    struct Entry { int device; float l1, l2; float* tab; };
+    static std::mutex mu; static std::vector<Entry> cache;
+    int dev = 0; NGP_CUDA_CHECK(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> lock(mu);
+    for (const Entry& e : cache) if (e.device == dev && e.l1 == ln_beta1 && e.l2 == ln_beta2) return e.tab;
+    float* tab = nullptr;
+    NGP_CUDA_CHECK(cudaMalloc(&tab, BIAS_TABLE_N * sizeof(float)));
+    bias_table_kernel<<<BIAS_TABLE_N / 256, 256, 0, s>>>(ln_beta1, ln_beta2, tab);
+    NGP_POST_LAUNCH();
+    NGP_CUDA_CHECK(cudaStreamSynchronize(s));      // once: later steps may come from other streams
+    cache.push_back({dev, ln_beta1, ln_beta2, tab});
+    return tab;
 }
 
 void adam_step(cudaStream_t s, const AdamHyper& h, uint64_t n, float* master, __half* params, const __half* grads, float* m, float* v,
                uint32_t* steps, float* ema_f32, __half* ema_half) {
     if (n == 0) return;
     NGP_CHECK(h.n_matrix_params % 4 == 0, "adam_step: n_matrix_params must be a multiple of 4");
+    AdamConsts c{(float)std::log((double)h.beta1), (float)std::log((double)h.beta2), 0.f, 1.f, 1.0f / h.loss_scale, nullptr};
+    c.bias = bias_table(s, c.ln_beta1, c.ln_beta2);
     NGP_PROFILE_SCOPE(s, "adam", n);
-    AdamConsts c{(float)std::log((double)h.beta1), (float)std::log((double)h.beta2), 0.f, 1.f};
-    if (ema_f32) { c.ema_old_debias = 1.0f - powf(h.ema_decay, (float)(h.ema_step - 1)); c.ema_new_debias = 1.0f - powf(h.ema_decay, (float)h.ema_step); }
+    if (ema_f32) { c.ema_old_debias = 1.0f - powf(h.ema_decay, (float)(h.ema_step - 1)); c.inv_ema_new_debias = 1.0f / (1.0f - powf(h.ema_decay, (float)h.ema_step)); }
     const uint64_t threads = (n + 3) / 4;
     adam_kernel<<<(uint32_t)((threads + 255) / 256), 256, 0, s>>>(h, c, n, master, params, grads, m, v, steps, ema_f32, ema_half);
     NGP_POST_LAUNCH();

@@ -90,7 +90,7 @@ def _step_and_capture(tb, ref, env, n_warm):
     return rpb, max_inference, step
 
 
-@pytest.mark.parametrize("lanes", [1, 4, 8, 32])
+@pytest.mark.parametrize("lanes", [1, 2, 4, 8, 32])
 @pytest.mark.parametrize("n_warm", [0, 5])
 def test_sampler_and_loss_bit_exact_compaction(env, ref, n_warm, lanes):
     tb = _testbed(env, lanes)
@@ -136,7 +136,7 @@ def test_sampler_and_loss_bit_exact_compaction(env, ref, n_warm, lanes):
 def test_marcher_variants_train_identically(env):
     """thread-per-ray, 8 and 32 lanes per ray: same samples and sample counts at every step of a 40-step run"""
     params = []
-    for lanes in (1, 4, 8, 32):
+    for lanes in (1, 2, 4, 8, 32):
         tb = _testbed(env, lanes)
         for _ in range(40):
             tb.train(BATCH)

@@ -31,3 +31,8 @@ for m in marks:
     print(json.dumps({"step": step, "ms_per_step_wall": round(dt, 3), "rays_per_batch": st.rays_per_batch, "measured": st.measured_batch_size,
                       "before": st.measured_batch_size_before_compaction, "loss": st.loss, "psnr_view0": round(psnr(0), 2),
                       "kernels_ms_per_step": {k: round(v["ms"] / 32, 4) for k, v in prof.items()}}), flush=True)
+if os.environ.get('NGP_DUMP'):      # state of the last sampler launch, for offline analysis of the walk (tools/walk_stats.py)
+    c = tb.debug_tensor("counters", torch.int32, 4).cpu().numpy().view(np.uint32); nr = int(c[0])
+    np.savez_compressed(os.environ['NGP_DUMP'], counters=c, bitfield=tb.density_grid(1).cpu().numpy(),
+                        rays=tb.debug_tensor("rays", torch.float32, nr * 6).cpu().numpy().reshape(nr, 6),
+                        numsteps=tb.debug_tensor("numsteps", torch.int32, nr * 2).cpu().numpy().reshape(nr, 2))
