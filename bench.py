@@ -265,6 +265,8 @@ def run_own(args):
 
     # per-kernel CUDA-event timing on the launching stream over a third pass of K steps (events add ~2 records per kernel,
     # so this pass is not the one `value` comes from)
+    prefetch_hits = int(tb.prefetch_hits)
+    tb.prefetch_rays = False            # kernels timed one at a time: no ray prefetch running beside them on the second stream
     lib.ngp_profile_enable(1)
     buf = C.create_string_buffer(1 << 16)
     lib.ngp_profile_report(buf, len(buf), 1)
@@ -302,7 +304,7 @@ def run_own(args):
             "data": "synthetic",
             "config": {"workload": workload_name(args), "global_batch": batch * world, "per_gpu_batch": batch, "parallelism": f"dp{world}" if world > 1 else "single",
                        "pretrain_steps_untimed": args.pretrain, "samples_before_compaction_per_step": n_before / args.steps / world,
-                       "rays_per_batch": tb.stats.rays_per_batch, "n_params": int(tb.n_params()),
+                       "rays_per_batch": tb.stats.rays_per_batch, "n_params": int(tb.n_params()), "steps_with_prefetched_rays": prefetch_hits,
                        "l2_policy": "inputs larger than L2: 256 MB image set + 24 MB table + >100 MB sample buffers touched every step"},
             "e2e": {"value": n_e2e / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": view_bytes, "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / args.steps,
                     "api": "pyngp.Testbed.set_training_image + train + loss"},

@@ -170,7 +170,9 @@ int ngp_testbed_compute_image_mse(ngp_testbed_t t, void* stream, int32_t quantiz
  * "near_distance","density_grid_decay","render_min_transmittance","cone_angle_constant" (float),
  * "loss_type","rgb_activation","density_activation" (enum), "seed" (integer), "image_snap_to_pixel_centers",
  * "image_linear_colors","image_stratified" (bool), "background_r/g/b" (float),
- * "sampler_lanes_per_ray" (0 automatic | 1 | 8 | 32: lanes that cooperate on one training ray; results are identical) */
+ * "sampler_lanes_per_ray" (0 automatic | 1 | 2 | 4 | 8 | 32: lanes that cooperate on one training ray; results are identical),
+ * "prefetch_rays" (bool, default 1: the next step's rays are generated on a second stream beside this step's backward pass
+ * and optimizer whenever the next step does not refresh the occupancy grid first; results are identical) */
 int ngp_testbed_set_option(ngp_testbed_t t, const char* name, double value);
 /* parity hook: device pointer + capacity of an internal per-step buffer ("coords","numsteps","ray_indices","rays",
  * "counters","mlp_out","dloss","coords_compacted","loss","grid_pos","grid_idx","grid_out","mean_density",...) */

@@ -466,22 +466,41 @@ __global__ void __launch_bounds__(SCAN_BLOCK) sampler_write_kernel(uint32_t n_ra
 // K candidates (position, aabb test, dt, occupancy byte: K independent loads) and ballots tell where the hypothesis first
 // fails.  The chain loop carries no aabb test and no capture beyond one select: candidates past the exit are computed and
 // ignored.  Warp instructions per ray scale with 1/rays-per-warp = G/32 at a fixed C, which is why K > 1 pays.
-template <bool FLAT, bool STEP>
+// FAST: the round starts at t in [1e-30, 1024); a round moves t by at most C * (one voxel diagonal / 128 + one step) < 1,
+// so every t of the round is inside the range where div_by_stepsize takes its branch-free form, and the test is made once
+// per round instead of once per division.
+NGP_D float div_by_stepsize_in_range(float t) {
+    constexpr float S = SQRT3 / (float)NERF_STEPS, RS = 1.0f / S;
+    const float q = t * RS; return fmaf(fmaf(-q, S, t), RS, q);
+}
+template <bool FLAT, bool STEP, bool FAST>
 NGP_D float chain_next(float t, const RayConst& rc, float cone, uint32_t max_mip) {
+    if (FLAT && FAST) {
+        const float n = div_by_stepsize_in_range(t);
+        if (STEP) return t + ((n + 1.0f) * MIN_CONE_STEPSIZE() - t);
+        const V3 pos = ray_at(rc.o, rc.d, t);
+        const V3 p = (float)NERF_GRIDSIZE * (pos - v3(0.5f, 0.5f, 0.5f));
+        const float tx = (floorf(p.x + 0.5f + rc.hs.x) - p.x) * rc.idir.x;
+        const float ty = (floorf(p.y + 0.5f + rc.hs.y) - p.y) * rc.idir.y;
+        const float tz = (floorf(p.z + 0.5f + rc.hs.z) - p.z) * rc.idir.z;
+        const float dist = fmaxf(fminf(fminf(tx, ty), tz) * (1.0f / (float)NERF_GRIDSIZE), 0.0f);
+        const float nt = div_by_stepsize_in_range(t + dist);
+        return (n + ceilf(fmaxf(nt - n, 0.5f))) * MIN_CONE_STEPSIZE();
+    }
     if (FLAT && STEP) { const float n = div_by_stepsize(t); return t + ((n + 1.0f) * MIN_CONE_STEPSIZE() - t); }
     const V3 pos = ray_at(rc.o, rc.d, t);
     float dt, n; uint32_t mip;
     candidate_dt_mip<FLAT>(t, pos, cone, max_mip, dt, mip, n);
     return STEP ? t + dt : candidate_skip<FLAT>(t, n, pos, rc, cone, mip);
 }
-template <uint32_t G, uint32_t K, bool FLAT, bool STEP>
+template <uint32_t G, uint32_t K, bool FLAT, bool STEP, bool FAST>
 NGP_D float chain_round(float t, float* my_t, uint32_t lane, const RayConst& rc, float cone, uint32_t max_mip) {
 #pragma unroll
     for (uint32_t k = 0; k < K; ++k) {
 #pragma unroll (G < 8 ? G : 8)
         for (uint32_t g = 0; g < G; ++g) {
             if (g == lane) my_t[k] = t;
-            t = chain_next<FLAT, STEP>(t, rc, cone, max_mip);
+            t = chain_next<FLAT, STEP, FAST>(t, rc, cone, max_mip);
         }
     }
     return t;
@@ -499,8 +518,13 @@ NGP_D uint32_t march_training_ray_group(V3 o, V3 d, float startt, float cone, co
     uint32_t j = 0; float t_base = startt; bool step_mode = false;
     while (true) {
         float my_t[K], my_dt[K];
-        const float t_end = step_mode ? chain_round<G, K, FLAT, true>(t_base, my_t, lane, rc, cone, max_mip)
-                                      : chain_round<G, K, FLAT, false>(t_base, my_t, lane, rc, cone, max_mip);
+        float t_end;
+        if (FLAT && t_base >= 1e-30f && t_base < 1024.0f)
+            t_end = step_mode ? chain_round<G, K, FLAT, true, true>(t_base, my_t, lane, rc, cone, max_mip)
+                              : chain_round<G, K, FLAT, false, true>(t_base, my_t, lane, rc, cone, max_mip);
+        else
+            t_end = step_mode ? chain_round<G, K, FLAT, true, false>(t_base, my_t, lane, rc, cone, max_mip)
+                              : chain_round<G, K, FLAT, false, false>(t_base, my_t, lane, rc, cone, max_mip);
         uint32_t in_mask = 0, occ_mask = 0;
 #pragma unroll
         for (uint32_t k = 0; k < K; ++k) {
@@ -548,7 +572,7 @@ NGP_D uint32_t march_training_ray_group(V3 o, V3 d, float startt, float cone, co
             float tf = my_t[0];
 #pragma unroll
             for (uint32_t k = 1; k < K; ++k) if (k == f / G) tf = my_t[k];
-            const float my_skip = chain_next<FLAT, false>(tf, rc, cone, max_mip);
+            const float my_skip = chain_next<FLAT, false, false>(tf, rc, cone, max_mip);
             t_base = __shfl_sync(gmask, my_skip, gshift + f % G);
             step_mode = false;
         } else {

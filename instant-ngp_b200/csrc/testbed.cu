@@ -18,7 +18,13 @@ Testbed::Testbed(int mode) : m_mode(mode), m_rng(1337), m_density_grid_rng(1337)
     NGP_CHECK(mode == MODE_TB_NERF || mode == MODE_TB_IMAGE, "Testbed: only the Nerf and Image modes are implemented on this path");
 }
 
-Testbed::~Testbed() { for (void* p : m_image_buffers) cudaFree(p); }
+Testbed::~Testbed() {
+    if (m_aux_stream) { cudaStreamSynchronize(m_aux_stream); cudaStreamDestroy(m_aux_stream); }
+    if (m_ev_counters) cudaEventDestroy(m_ev_counters);
+    if (m_ev_prefetch) cudaEventDestroy(m_ev_prefetch);
+    if (m_host_counters) cudaFreeHost(m_host_counters);
+    for (void* p : m_image_buffers) cudaFree(p);
+}
 
 void Testbed::reload_network_from_json(const std::string& json) {
     Json patch = Json::parse(json);
@@ -59,6 +65,8 @@ void Testbed::set_nerf_dataset(cudaStream_t s, uint32_t n_images, const HostImag
     NGP_CHECK(n_images > 0 && images, "set_nerf_dataset: no images");
     NGP_CHECK(aabb_scale >= 1 && (aabb_scale & (aabb_scale - 1)) == 0, "NeRF dataset's `aabb_scale` must be a power of two");
     NGP_CHECK(aabb_scale <= (1 << (NERF_CASCADES - 1)), "NeRF dataset must have `aabb_scale <= 128`");
+    if (m_aux_stream) NGP_CUDA_CHECK(cudaStreamSynchronize(m_aux_stream));   // a ray prefetch in flight reads the old images
+    m_prefetch_valid = false; ++m_dataset_version; m_all_images_u8 = true;
     for (void* p : m_image_buffers) cudaFree(p);
     m_image_buffers.clear(); m_image_bytes.clear();
     std::vector<ImageMeta> metas(n_images);
@@ -67,6 +75,7 @@ void Testbed::set_nerf_dataset(cudaStream_t s, uint32_t n_images, const HostImag
         NGP_CHECK(h.data_type == IMG_BYTE || h.data_type == IMG_FLOAT, "image data type must be RGBA8 (0) or RGBA float32 (1)");
         NGP_CHECK(h.lens_mode == LENS_PERSPECTIVE || h.lens_mode == LENS_OPENCV, "lens mode must be Perspective (0) or OpenCV (1)");
         const size_t bytes = (size_t)h.res[0] * h.res[1] * (h.data_type == IMG_BYTE ? 4 : 16);
+        m_all_images_u8 = m_all_images_u8 && h.data_type == IMG_BYTE;
         void* d = nullptr;
         NGP_CUDA_CHECK(cudaMalloc(&d, bytes));
         m_image_buffers.push_back(d); m_image_bytes.push_back(bytes);
@@ -104,6 +113,7 @@ void Testbed::set_training_image(cudaStream_t s, uint32_t frame_idx, const void*
     NGP_CHECK(m_mode == MODE_TB_NERF, "set_training_image: testbed is not in Nerf mode");
     NGP_CHECK(frame_idx < m_n_images, "Invalid frame index");   // python_api.cu:50-52
     NGP_CHECK(pixels_host, "set_training_image: null pixels");
+    if (!m_all_images_u8) { ++m_dataset_version; if (m_aux_stream) NGP_CUDA_CHECK(cudaStreamSynchronize(m_aux_stream)); }   // RGBA8 has no masked (negative) pixels: the walk never depends on its content
     NGP_CUDA_CHECK(cudaMemcpyAsync(m_image_buffers[frame_idx], pixels_host, m_image_bytes[frame_idx], cudaMemcpyHostToDevice, s));
 }
 
@@ -183,21 +193,27 @@ void Testbed::train_end(cudaStream_t s, uint32_t measured_override, uint32_t mea
         NGP_CUDA_CHECK(cudaStreamSynchronize(s));
         return;
     }
-    // NerfCounters::update_after_training (testbed_nerf.cu:3583-3609): two counters (+ the loss every 16 steps) read back
-    if (m_get_loss) reduce_sum_f32(s, m_loss.as<float>(), m_rays_per_batch, m_loss_sum.as<float>(), m_partials.as<float>());
-    uint32_t c[4] = {0, 0, 0, 0}; float loss_sum = 0.f;
-    NGP_CUDA_CHECK(cudaMemcpyAsync(c, m_counters.as<uint32_t>(), sizeof(c), cudaMemcpyDeviceToHost, s));
-    if (m_get_loss) NGP_CUDA_CHECK(cudaMemcpyAsync(&loss_sum, m_loss_sum.as<float>(), 4, cudaMemcpyDeviceToHost, s));
-    NGP_CUDA_CHECK(cudaStreamSynchronize(s));
+    // NerfCounters::update_after_training (testbed_nerf.cu:3583-3609): two counters (+ the loss every 16 steps) read back.
+    // The counters were copied to pinned memory right after the loss kernel (train_nerf_step), so the host has them while
+    // the backward pass and the optimizer are still running: time enough to start the next step's rays beside them.
+    if (m_get_loss) {
+        reduce_sum_f32(s, m_loss.as<float>(), m_rays_per_batch, m_loss_sum.as<float>(), m_partials.as<float>());
+        NGP_CUDA_CHECK(cudaMemcpyAsync(m_host_counters + 4, m_loss_sum.as<float>(), 4, cudaMemcpyDeviceToHost, s));
+    }
+    NGP_CUDA_CHECK(cudaEventSynchronize(m_ev_counters));
+    const uint32_t* c = m_host_counters;
     m_measured_before = measured_before_override ? measured_before_override : c[1];
     m_measured = measured_override ? measured_override : c[2];
     if (m_measured_before == 0 || m_measured == 0) {
         m_measured = m_measured_before = 0; m_loss_scalar = 0.f;
+        cudaStreamSynchronize(s);
         throw Error("Nerf training generated 0 samples. Aborting training.");   // testbed_nerf.cu:3693-3697
     }
-    if (m_get_loss) m_loss_scalar = loss_sum * (float)m_measured / (float)target;
     m_rays_per_batch = (uint32_t)((float)m_rays_per_batch * (float)target / (float)m_measured);
     m_rays_per_batch = std::min((uint32_t)next_multiple(m_rays_per_batch, BATCH_GRANULARITY), 1u << 18);
+    launch_ray_prefetch(s, target);
+    NGP_CUDA_CHECK(cudaStreamSynchronize(s));
+    if (m_get_loss) { float loss_sum; memcpy(&loss_sum, m_host_counters + 4, 4); m_loss_scalar = loss_sum * (float)m_measured / (float)target; }
 }
 
 TrainStats Testbed::stats() const {
@@ -213,24 +229,75 @@ TrainStats Testbed::stats() const {
 // ---------------------------------------------------------------------------------------------------------------
 // train_nerf_step (testbed_nerf.cu:3867-4132)
 // ---------------------------------------------------------------------------------------------------------------
-void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
-    NGP_PROFILE_SCOPE(s, "train_nerf_step");
+Testbed::SamplerKey Testbed::sampler_key(uint32_t n_rays, uint32_t max_inference, uint32_t target) const {
+    return {m_training_step, n_rays, max_inference, target, m_rank, m_world, sampler_lanes_per_ray, m_dataset_version, m_rng.state, m_rng.inc,
+            cone_angle_constant, snap_to_pixel_centers};
+}
+
+SamplerBuffers Testbed::sampler_buffers(cudaStream_t s, uint32_t set, uint32_t target, uint32_t n_rays) {
     const uint32_t max_samples = target * 16;   // "somewhat of a worst case" (:3873)
-    const uint32_t R = m_rays_per_batch, max_rays = 1u << 18;
+    const uint32_t max_rays = 1u << 18;
     const uint32_t max_blocks = max_rays / 8 + 1;   // 256 / lanes_per_ray rays per block, lanes_per_ray <= 32
     SamplerBuffers sb{};
-    sb.numsteps_all = m_numsteps_all.get<uint32_t>(max_rays); sb.block_steps = m_block_steps.get<uint32_t>(max_blocks);
-    sb.block_rays = m_block_rays.get<uint32_t>(max_blocks); sb.ray_tmp = m_ray_tmp.get<float>((size_t)max_rays * 8);
-    sb.ray_indices = m_ray_indices.get<uint32_t>(max_rays); sb.rays = m_rays.get<float>((size_t)max_rays * 6);
-    sb.numsteps = m_numsteps.get<uint32_t>((size_t)max_rays * 2);
-    const bool fresh_coords = m_coords.bytes < (size_t)max_samples * 7 * 4;
-    sb.coords = m_coords.get<float>((size_t)max_samples * 7);
+    sb.numsteps_all = m_numsteps_all[set].get<uint32_t>(max_rays); sb.block_steps = m_block_steps[set].get<uint32_t>(max_blocks);
+    sb.block_rays = m_block_rays[set].get<uint32_t>(max_blocks); sb.ray_tmp = m_ray_tmp[set].get<float>((size_t)max_rays * 8);
+    sb.ray_indices = m_ray_indices[set].get<uint32_t>(max_rays); sb.rays = m_rays[set].get<float>((size_t)max_rays * 6);
+    sb.numsteps = m_numsteps[set].get<uint32_t>((size_t)max_rays * 2);
+    const bool fresh_coords = m_coords[set].bytes < (size_t)max_samples * 7 * 4;
+    sb.coords = m_coords[set].get<float>((size_t)max_samples * 7);
     if (fresh_coords) NGP_CUDA_CHECK(cudaMemsetAsync(sb.coords, 0, (size_t)max_samples * 7 * 4, s));   // stale rows are fed to the network: keep them finite
-    sb.counters = m_counters.get<uint32_t>(4);
+    sb.counters = m_counters[set].get<uint32_t>(4);
     sb.lanes_per_ray = sampler_lanes_per_ray;
-    sb.sample_scratch = m_sample_scratch.get<float2>(max_samples);
-    sb.scratch_per_ray = std::min<uint32_t>(NERF_STEPS, max_samples / R);
-    sb.pool_slots = 4096; sb.sample_pool = m_sample_pool.get<float2>((size_t)sb.pool_slots * NERF_STEPS); sb.overflow_slot = m_overflow_slot.get<uint32_t>(max_rays);
+    sb.sample_scratch = m_sample_scratch[set].get<float2>(max_samples);
+    sb.scratch_per_ray = std::min<uint32_t>(NERF_STEPS, max_samples / n_rays);
+    sb.pool_slots = 4096; sb.sample_pool = m_sample_pool[set].get<float2>((size_t)sb.pool_slots * NERF_STEPS);
+    sb.overflow_slot = m_overflow_slot[set].get<uint32_t>(max_rays);
+    return sb;
+}
+
+uint32_t Testbed::max_inference_samples(uint32_t target) {
+    const uint32_t max_samples = target * 16;
+    if (m_measured_before == 0) return m_measured_before = max_samples;
+    return (uint32_t)next_multiple(std::min(m_measured_before, max_samples), BATCH_GRANULARITY);
+}
+
+// prepare_for_training_steps (:3569-3581) + generate_training_samples_nerf (:1382-1658)
+void Testbed::launch_sampler(cudaStream_t s, const SamplerKey& key, const SamplerBuffers& sb) {
+    NGP_CUDA_CHECK(cudaMemsetAsync(sb.counters, 0, 16, s));
+    nerf_generate_training_samples(s, key.n_rays, aabb, key.max_inference, 0, m_rng, m_n_images, m_metas.as<ImageMeta>(), m_bitfield.as<uint8_t>(), m_max_cascade,
+                                   snap_to_pixel_centers, cone_angle_constant, m_rank * key.n_rays, m_world * key.n_rays, sb);
+}
+
+// The rays of step N + 1 depend on the rng, the control law's rays_per_batch (known once step N's loss has run) and the
+// occupancy bitfield — not on the weights.  When step N + 1 will not refresh the bitfield first, its walk is started here
+// on a second stream, beside step N's backward pass / optimizer (latency-bound traversal next to HBM- and atomics-bound
+// kernels), into the buffer set step N does not use.  train_nerf_step(N + 1) adopts it only if every input still matches.
+void Testbed::launch_ray_prefetch(cudaStream_t s, uint32_t target) {
+    if (!prefetch_rays || m_mode != MODE_TB_NERF || !m_all_images_u8) return;
+    const uint32_t n_prep_to_skip = std::min(std::max(m_training_step / 16u, 1u), 16u);
+    if (m_training_step % n_prep_to_skip == 0) return;      // the next step starts with training_prep_nerf (new bitfield)
+    const uint32_t R = m_rays_per_batch, set = m_training_step & 1u;
+    const SamplerKey key = sampler_key(R, max_inference_samples(target), target);
+    NGP_CUDA_CHECK(cudaStreamWaitEvent(m_aux_stream, m_ev_counters, 0));   // after this step's loss (and everything before it) on `s`
+    const SamplerBuffers sb = sampler_buffers(m_aux_stream, set, target, R);
+    launch_sampler(m_aux_stream, key, sb);
+    NGP_CUDA_CHECK(cudaEventRecord(m_ev_prefetch, m_aux_stream));
+    m_prefetch_key = key; m_prefetch_valid = true;
+}
+
+void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
+    NGP_PROFILE_SCOPE(s, "train_nerf_step");
+    if (!m_aux_stream) {
+        NGP_CUDA_CHECK(cudaStreamCreateWithFlags(&m_aux_stream, cudaStreamNonBlocking));
+        NGP_CUDA_CHECK(cudaEventCreateWithFlags(&m_ev_counters, cudaEventDisableTiming));
+        NGP_CUDA_CHECK(cudaEventCreateWithFlags(&m_ev_prefetch, cudaEventDisableTiming));
+        NGP_CUDA_CHECK(cudaMallocHost(&m_host_counters, 8 * sizeof(uint32_t)));
+    }
+    const uint32_t max_samples = target * 16;
+    const uint32_t R = m_rays_per_batch, max_rays = 1u << 18;
+    const uint32_t set = m_training_step & 1u;
+    m_last_set = set;
+    const SamplerBuffers sb = sampler_buffers(s, set, target, R);
     LossBuffers lb{};
     __half* mlp_out = m_mlp_out.get<__half>((size_t)max_samples * 4);
     lb.network_output = mlp_out; lb.dloss_doutput = m_dloss.get<__half>((size_t)target * 4);
@@ -239,20 +306,18 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
     m_loss_sum.get<float>(4);
     lb.enc_width = m_nerf_net->dims.pos_width; lb.enc_out = m_nerf_net->training_encoding(target);
 
-    uint32_t max_inference;
-    if (m_measured_before == 0) { m_measured_before = max_inference = max_samples; }
-    else max_inference = (uint32_t)next_multiple(std::min(m_measured_before, max_samples), BATCH_GRANULARITY);
+    const uint32_t max_inference = max_inference_samples(target);
     if (m_training_step == 0) m_n_rays_total = 0;
     const uint32_t n_rays_total = m_n_rays_total;
     m_n_rays_total += R;
 
-    // prepare_for_training_steps (:3569-3581)
-    NGP_CUDA_CHECK(cudaMemsetAsync(sb.counters, 0, 16, s));
+    const SamplerKey key = sampler_key(R, max_inference, target);
+    const bool prefetched = m_prefetch_valid && m_prefetch_key == key;
+    if (m_prefetch_valid) NGP_CUDA_CHECK(cudaStreamWaitEvent(s, m_ev_prefetch, 0));   // adopted or stale, it must have left the buffers
+    m_prefetch_valid = false;
+    if (prefetched) ++prefetch_hits; else launch_sampler(s, key, sb);
     NGP_CUDA_CHECK(cudaMemsetAsync(lb.loss, 0, sizeof(float) * R, s));
-
     const uint32_t ray_offset = m_rank * R, n_rays_global = m_world * R;
-    nerf_generate_training_samples(s, R, aabb, max_inference, n_rays_total, m_rng, m_n_images, m_metas.as<ImageMeta>(), m_bitfield.as<uint8_t>(), m_max_cascade,
-                                   snap_to_pixel_centers, cone_angle_constant, ray_offset, n_rays_global, sb);
     m_nerf_net->inference(s, m_trainer->params, sb.coords, max_inference, mlp_out);   // inference_mixed_precision(.., use_inference_params=false) (:4001)
 
     LossConfig lc{};
@@ -262,6 +327,8 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
     lc.loss_scale = LOSS_SCALE; lc.near_distance = near_distance;
     lb.enc_in = m_nerf_net->last_inference_encoding();   // written by inference() just above
     nerf_compute_loss(s, R, aabb, n_rays_total, m_rng, target, lc, m_n_images, m_metas.as<ImageMeta>(), m_mean.as<float>(), ray_offset, n_rays_global, sb, lb);
+    NGP_CUDA_CHECK(cudaMemcpyAsync(m_host_counters, sb.counters, 16, cudaMemcpyDeviceToHost, s));   // read by train_end
+    NGP_CUDA_CHECK(cudaEventRecord(m_ev_counters, s));
     nerf_fill_rollover(s, target, &sb.counters[2], lb.dloss_doutput, lb.coords_compacted, lb.enc_out, lb.enc_width);   // :4061-4069
     // forward(compacted) + backward(EGradientMode::Overwrite) (:4077-4078)
     m_nerf_net->forward_backward_encoded(s, m_trainer->params, lb.coords_compacted, target, lb.dloss_doutput, m_trainer->grads);
@@ -361,10 +428,11 @@ void Testbed::render(cudaStream_t s, const float* camera_matrix, const float* fo
 
 void Testbed::debug_buffer(const std::string& name, void** ptr, uint64_t* bytes) {
     struct E { const char* n; DeviceBuffer* b; };
-    const E table[] = {{"coords", &m_coords}, {"numsteps", &m_numsteps}, {"ray_indices", &m_ray_indices}, {"rays", &m_rays}, {"counters", &m_counters},
+    const uint32_t k = m_last_set;   // the buffer set the last training step used (the other one may hold the next step's prefetch)
+    const E table[] = {{"coords", &m_coords[k]}, {"numsteps", &m_numsteps[k]}, {"ray_indices", &m_ray_indices[k]}, {"rays", &m_rays[k]}, {"counters", &m_counters[k]},
                        {"mlp_out", &m_mlp_out}, {"dloss", &m_dloss}, {"coords_compacted", &m_coords_compacted}, {"loss", &m_loss},
                        {"grid_pos", &m_grid_pos}, {"grid_idx", &m_grid_idx}, {"grid_out", &m_grid_out}, {"density_grid_tmp", &m_density_grid_tmp},
-                       {"mean_density", &m_mean}, {"numsteps_all", &m_numsteps_all}, {"image_pos", &m_img_pos}, {"image_target", &m_img_target},
+                       {"mean_density", &m_mean}, {"numsteps_all", &m_numsteps_all[k]}, {"image_pos", &m_img_pos}, {"image_target", &m_img_target},
                        {"image_out", &m_img_out}, {"image_dl", &m_img_dl}};
     for (const E& e : table) if (name == e.n) { *ptr = e.b->ptr; *bytes = e.b->bytes; return; }
     throw Error("debug_buffer: unknown buffer '" + name + "'");

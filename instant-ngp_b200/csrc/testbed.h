@@ -64,7 +64,11 @@ public:
     int loss_type = LOSS_L2, rgb_activation = ACT_LOGISTIC, density_activation = ACT_EXPONENTIAL;
     bool image_snap_to_pixel_centers = true, image_linear_colors = false, image_stratified = true;
     uint64_t seed = 1337;
-    uint32_t sampler_lanes_per_ray = 0;   // 0 = automatic; 1 / 8 / 32 force a marcher variant (parity tests)
+    uint32_t sampler_lanes_per_ray = 0;   // 0 = automatic; 1 / 2 / 4 / 8 / 32 force a marcher variant (parity tests)
+    // generate the NEXT step's rays on a second stream while this step's backward pass and optimizer run (the walk depends on
+    // the occupancy bitfield and the rng only, not on the weights); same samples either way, see launch_ray_prefetch()
+    bool prefetch_rays = true;
+    uint32_t prefetch_hits = 0;   // read-only: steps whose rays came from a prefetch
     Aabb aabb{{0, 0, 0}, {1, 1, 1}}, render_aabb{{0, 0, 0}, {1, 1, 1}};
 
 private:
@@ -73,6 +77,18 @@ private:
     void update_density_grid_nerf(cudaStream_t s, float decay, uint32_t n_uniform, uint32_t n_nonuniform);   // :3412-3536
     void train_nerf_step(cudaStream_t s, uint32_t target_batch_size);                              // :3867-4132
     void train_image_step(cudaStream_t s, uint32_t batch_size, bool get_loss);                     // testbed_image.cu:214-285
+    struct SamplerKey {   // everything generate_training_samples depends on besides the bitfield and the view poses
+        uint32_t step, n_rays, max_inference, target, rank, world, lanes, dataset_version; uint64_t rng_state, rng_inc; float cone; bool snap;
+        bool operator==(const SamplerKey& o) const {
+            return step == o.step && n_rays == o.n_rays && max_inference == o.max_inference && target == o.target && rank == o.rank && world == o.world &&
+                   lanes == o.lanes && dataset_version == o.dataset_version && rng_state == o.rng_state && rng_inc == o.rng_inc && cone == o.cone && snap == o.snap;
+        }
+    };
+    SamplerKey sampler_key(uint32_t n_rays, uint32_t max_inference, uint32_t target) const;
+    SamplerBuffers sampler_buffers(cudaStream_t s, uint32_t set, uint32_t target, uint32_t n_rays);
+    uint32_t max_inference_samples(uint32_t target);
+    void launch_sampler(cudaStream_t s, const SamplerKey& key, const SamplerBuffers& sb);
+    void launch_ray_prefetch(cudaStream_t s, uint32_t target);
 
     int m_mode;
     Json m_config; bool m_have_config = false;
@@ -91,8 +107,13 @@ private:
     // NerfCounters (testbed.h:433-447)
     uint32_t m_rays_per_batch = 1u << 12, m_n_rays_total = 0, m_measured = 0, m_measured_before = 0;
     // per-step scratch
-    DeviceBuffer m_numsteps_all, m_block_steps, m_block_rays, m_ray_tmp, m_ray_indices, m_rays, m_numsteps, m_coords, m_counters, m_mlp_out, m_dloss,
-        m_coords_compacted, m_loss, m_ray_scratch, m_compacted_numsteps, m_loss_sum, m_sample_scratch, m_sample_pool, m_overflow_slot;
+    // sampler outputs and scratch exist twice: step N reads set N & 1 while the prefetch of step N + 1 fills the other one
+    DeviceBuffer m_numsteps_all[2], m_block_steps[2], m_block_rays[2], m_ray_tmp[2], m_ray_indices[2], m_rays[2], m_numsteps[2], m_coords[2], m_counters[2],
+        m_sample_scratch[2], m_sample_pool[2], m_overflow_slot[2];
+    DeviceBuffer m_mlp_out, m_dloss, m_coords_compacted, m_loss, m_ray_scratch, m_compacted_numsteps, m_loss_sum;
+    cudaStream_t m_aux_stream = nullptr; cudaEvent_t m_ev_counters = nullptr, m_ev_prefetch = nullptr;
+    uint32_t* m_host_counters = nullptr;   // pinned: 4 counters + the loss sum
+    bool m_prefetch_valid = false, m_all_images_u8 = false; SamplerKey m_prefetch_key{}; uint32_t m_dataset_version = 0, m_last_set = 0;
     // image mode
     DeviceBuffer m_image; int m_image_w = 0, m_image_h = 0; DeviceBuffer m_img_pos, m_img_target, m_img_out, m_img_dl, m_img_loss;
     // render scratch

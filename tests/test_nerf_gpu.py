@@ -29,9 +29,10 @@ def env(ngp, ref):
     return dict(pyngp=pyngp, scene=scene, views=views, images=images, keep=keep)
 
 
-def _testbed(env, lanes=0):
+def _testbed(env, lanes=0, prefetch=True):
     tb = env["pyngp"].Testbed(env["pyngp"].TestbedMode.Nerf)
-    tb.sampler_lanes_per_ray = lanes     # 0 automatic; 1 / 8 / 32 lanes cooperate on one ray (identical results)
+    tb.sampler_lanes_per_ray = lanes     # 0 automatic; 1 / 2 / 4 / 8 / 32 lanes cooperate on one ray (identical results)
+    tb.prefetch_rays = prefetch          # next step's rays generated beside this step's backward pass (identical results)
     tb.set_nerf_dataset(env["views"], aabb_scale=1)
     tb.reload_network_from_json(SMALL_CFG)
     return tb
@@ -90,11 +91,14 @@ def _step_and_capture(tb, ref, env, n_warm):
     return rpb, max_inference, step
 
 
-@pytest.mark.parametrize("lanes", [1, 2, 4, 8, 32])
-@pytest.mark.parametrize("n_warm", [0, 5])
-def test_sampler_and_loss_bit_exact_compaction(env, ref, n_warm, lanes):
-    tb = _testbed(env, lanes)
+@pytest.mark.parametrize("n_warm,lanes,prefetch", [(w, l, True) for w in (0, 5) for l in (1, 2, 4, 8, 32)] + [(37, 0, True), (37, 0, False), (51, 8, True)])
+def test_sampler_and_loss_bit_exact_compaction(env, ref, n_warm, lanes, prefetch):
+    """n_warm >= 33 and odd: the captured step does not refresh the occupancy grid, so with prefetch its rays were generated
+    on the second stream during the step before"""
+    tb = _testbed(env, lanes, prefetch)
     rpb, max_inf, step = _step_and_capture(tb, ref, env, n_warm)
+    if n_warm > 32:
+        assert (tb.prefetch_hits > 0) == prefetch
     aabb = ref.make_aabb((0, 0, 0), (1, 1, 1))
     bf = tb.density_grid(1).cpu().numpy()
     skip = 1 + step * (1 << 32)
@@ -136,8 +140,8 @@ def test_sampler_and_loss_bit_exact_compaction(env, ref, n_warm, lanes):
 def test_marcher_variants_train_identically(env):
     """thread-per-ray, 8 and 32 lanes per ray: same samples and sample counts at every step of a 40-step run"""
     params = []
-    for lanes in (1, 2, 4, 8, 32):
-        tb = _testbed(env, lanes)
+    for lanes, prefetch in ((1, False), (2, True), (4, True), (8, True), (32, True), (0, False), (0, True)):
+        tb = _testbed(env, lanes, prefetch)
         for _ in range(40):
             tb.train(BATCH)
         params.append((tb.param_buffer(0).cpu().numpy().copy(), tb.stats.rays_per_batch, tb.stats.measured_batch_size))

@@ -9,7 +9,7 @@ lib = importlib.import_module("instant-ngp_b200._lib").lib()
 nv, res = int(sys.argv[1]) if len(sys.argv) > 1 else 100, int(sys.argv[2]) if len(sys.argv) > 2 else 800
 views = scene.make_views(nv, res, res)
 tb = pyngp.Testbed(pyngp.TestbedMode.Nerf); tb.set_nerf_dataset(views, aabb_scale=1); tb.reload_network_from_json(bench.network_config(19))
-tb.sampler_lanes_per_ray = int(os.environ.get('NGP_LANES', '0'))
+tb.sampler_lanes_per_ray = int(os.environ.get('NGP_LANES', '0')); tb.prefetch_rays = os.environ.get('NGP_PREFETCH', '1') == '1'
 buf = C.create_string_buffer(1 << 16)
 def psnr(view):
     v = views[view]; W = 200; f = scene.focal_px(W)
