@@ -212,8 +212,13 @@ void Testbed::train_end(cudaStream_t s, uint32_t measured_override, uint32_t mea
     m_rays_per_batch = (uint32_t)((float)m_rays_per_batch * (float)target / (float)m_measured);
     m_rays_per_batch = std::min((uint32_t)next_multiple(m_rays_per_batch, BATCH_GRANULARITY), 1u << 18);
     launch_ray_prefetch(s, target);
-    NGP_CUDA_CHECK(cudaStreamSynchronize(s));
-    if (m_get_loss) { float loss_sum; memcpy(&loss_sum, m_host_counters + 4, 4); m_loss_scalar = loss_sum * (float)m_measured / (float)target; }
+    // No host wait for the optimizer: the control law only needed the counters (already here), and everything that consumes
+    // the new weights is ordered behind them on `s`.  The host so runs half a step ahead and the device never idles between
+    // steps.  Only the loss read-back (every 16th step) has to wait for its reduction.
+    if (m_get_loss) {
+        NGP_CUDA_CHECK(cudaStreamSynchronize(s));
+        float loss_sum; memcpy(&loss_sum, m_host_counters + 4, 4); m_loss_scalar = loss_sum * (float)m_measured / (float)target;
+    }
 }
 
 TrainStats Testbed::stats() const {
@@ -288,7 +293,10 @@ void Testbed::launch_ray_prefetch(cudaStream_t s, uint32_t target) {
 void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
     NGP_PROFILE_SCOPE(s, "train_nerf_step");
     if (!m_aux_stream) {
-        NGP_CUDA_CHECK(cudaStreamCreateWithFlags(&m_aux_stream, cudaStreamNonBlocking));
+        int least = 0, greatest = 0;
+        NGP_CUDA_CHECK(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+        const char* pe = getenv("NGP_AUX_PRIORITY");
+        NGP_CUDA_CHECK(cudaStreamCreateWithPriority(&m_aux_stream, cudaStreamNonBlocking, pe && atoi(pe) ? greatest : least));
         NGP_CUDA_CHECK(cudaEventCreateWithFlags(&m_ev_counters, cudaEventDisableTiming));
         NGP_CUDA_CHECK(cudaEventCreateWithFlags(&m_ev_prefetch, cudaEventDisableTiming));
         NGP_CUDA_CHECK(cudaMallocHost(&m_host_counters, 8 * sizeof(uint32_t)));

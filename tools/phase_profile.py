@@ -19,6 +19,8 @@ def psnr(view):
     return -10 * np.log10(max(float(((img[..., :3] - lin) ** 2).mean()), 1e-10))
 marks = [int(x) for x in (sys.argv[3].split(",") if len(sys.argv) > 3 else "64,256,512,1000,2000,4000".split(","))]
 step = 0
+if os.environ.get('NGP_MAIN_PRIORITY'):      # run the training stream above the prefetch stream
+    _hp = torch.cuda.Stream(priority=int(os.environ['NGP_MAIN_PRIORITY'])); torch.cuda.set_stream(_hp)
 for m in marks:
     while step < m: tb.train(1 << 18); step += 1
     lib.ngp_profile_enable(1); lib.ngp_profile_report(buf, len(buf), 1)
