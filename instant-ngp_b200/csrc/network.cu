@@ -112,7 +112,8 @@ void NerfNetwork::forward_backward(cudaStream_t s, const __half* params, const f
     grid_backward(s, grid, coords, 7, n, denc, LAYOUT_BLK8, grads + off_grid);
 }
 
-void NerfNetwork::forward_backward_encoded(cudaStream_t s, const __half* params, const float* coords, uint32_t n, const __half* dL_dout, __half* grads) {
+void NerfNetwork::forward_backward_encoded(cudaStream_t s, const __half* params, const float* coords, uint32_t n, const __half* dL_dout, __half* grads,
+                                           cudaEvent_t after_mlp) {
     const __half* enc = enc_train_buf.as<__half>();
     __half* denc = denc_buf.get<__half>((size_t)n * dims.pos_width);
     float* wg = wgrad_buf.get<float>(n_matrix_params);
@@ -120,6 +121,7 @@ void NerfNetwork::forward_backward_encoded(cudaStream_t s, const __half* params,
     NGP_CUDA_CHECK(cudaMemsetAsync(grads + off_grid, 0, grid.n_params * sizeof(__half), s));
     nerf_mlp_backward(s, dims, params + off_density, params + off_rgb, enc, coords, n, dL_dout, denc, wg);
     cast_f32_to_half(s, wg, grads, n_matrix_params);
+    if (after_mlp) NGP_CUDA_CHECK(cudaEventRecord(after_mlp, s));
     grid_backward(s, grid, coords, 7, n, denc, LAYOUT_BLK8, grads + off_grid);
 }
 

@@ -46,7 +46,8 @@ struct NerfNetwork {
     // forward(recompute)+backward; grads: param-shaped fp16, OVERWRITTEN (EGradientMode::Overwrite, testbed_nerf.cu:4078)
     void forward_backward(cudaStream_t s, const __half* params, const float* coords, uint32_t n, const __half* dL_dout, __half* grads);
     // same, with the encoder outputs of the n samples already known (blk8 rows in enc_train_buf, carried over from inference())
-    void forward_backward_encoded(cudaStream_t s, const __half* params, const float* coords, uint32_t n, const __half* dL_dout, __half* grads);
+    void forward_backward_encoded(cudaStream_t s, const __half* params, const float* coords, uint32_t n, const __half* dL_dout, __half* grads,
+                                  cudaEvent_t after_mlp = nullptr);   // recorded between the MLP and the hash-grid backward kernels
     const __half* last_inference_encoding() const { return enc_buf.as<__half>(); }
     __half* training_encoding(uint32_t n) { return enc_train_buf.get<__half>((size_t)n * dims.pos_width); }
 };

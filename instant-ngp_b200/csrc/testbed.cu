@@ -22,6 +22,7 @@ Testbed::~Testbed() {
     if (m_aux_stream) { cudaStreamSynchronize(m_aux_stream); cudaStreamDestroy(m_aux_stream); }
     if (m_ev_counters) cudaEventDestroy(m_ev_counters);
     if (m_ev_prefetch) cudaEventDestroy(m_ev_prefetch);
+    if (m_ev_after_mlp) cudaEventDestroy(m_ev_after_mlp);
     if (m_host_counters) cudaFreeHost(m_host_counters);
     for (void* p : m_image_buffers) cudaFree(p);
 }
@@ -283,7 +284,9 @@ void Testbed::launch_ray_prefetch(cudaStream_t s, uint32_t target) {
     if (m_training_step % n_prep_to_skip == 0) return;      // the next step starts with training_prep_nerf (new bitfield)
     const uint32_t R = m_rays_per_batch, set = m_training_step & 1u;
     const SamplerKey key = sampler_key(R, max_inference_samples(target), target);
-    NGP_CUDA_CHECK(cudaStreamWaitEvent(m_aux_stream, m_ev_counters, 0));   // after this step's loss (and everything before it) on `s`
+    // start beside the hash-grid backward pass and the optimizer (atomics- and HBM-bound, few issue slots used); the fused MLP
+    // backward kernel (latency-bound, 8 warps per SM) loses more from sharing its SMs than the overlap wins
+    NGP_CUDA_CHECK(cudaStreamWaitEvent(m_aux_stream, m_ev_after_mlp, 0));
     const SamplerBuffers sb = sampler_buffers(m_aux_stream, set, target, R);
     launch_sampler(m_aux_stream, key, sb);
     NGP_CUDA_CHECK(cudaEventRecord(m_ev_prefetch, m_aux_stream));
@@ -295,10 +298,10 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
     if (!m_aux_stream) {
         int least = 0, greatest = 0;
         NGP_CUDA_CHECK(cudaDeviceGetStreamPriorityRange(&least, &greatest));
-        const char* pe = getenv("NGP_AUX_PRIORITY");
-        NGP_CUDA_CHECK(cudaStreamCreateWithPriority(&m_aux_stream, cudaStreamNonBlocking, pe && atoi(pe) ? greatest : least));
+        NGP_CUDA_CHECK(cudaStreamCreateWithPriority(&m_aux_stream, cudaStreamNonBlocking, least));   // never ahead of the training stream
         NGP_CUDA_CHECK(cudaEventCreateWithFlags(&m_ev_counters, cudaEventDisableTiming));
         NGP_CUDA_CHECK(cudaEventCreateWithFlags(&m_ev_prefetch, cudaEventDisableTiming));
+        NGP_CUDA_CHECK(cudaEventCreateWithFlags(&m_ev_after_mlp, cudaEventDisableTiming));
         NGP_CUDA_CHECK(cudaMallocHost(&m_host_counters, 8 * sizeof(uint32_t)));
     }
     const uint32_t max_samples = target * 16;
@@ -339,7 +342,7 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
     NGP_CUDA_CHECK(cudaEventRecord(m_ev_counters, s));
     nerf_fill_rollover(s, target, &sb.counters[2], lb.dloss_doutput, lb.coords_compacted, lb.enc_out, lb.enc_width);   // :4061-4069
     // forward(compacted) + backward(EGradientMode::Overwrite) (:4077-4078)
-    m_nerf_net->forward_backward_encoded(s, m_trainer->params, lb.coords_compacted, target, lb.dloss_doutput, m_trainer->grads);
+    m_nerf_net->forward_backward_encoded(s, m_trainer->params, lb.coords_compacted, target, lb.dloss_doutput, m_trainer->grads, m_ev_after_mlp);
     m_rng.advance();   // :4127
 }
 
