@@ -51,18 +51,23 @@ __global__ void __launch_bounds__(256) adam_kernel(const AdamHyper h, const Adam
     const uint64_t i0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
     if (i0 >= n) return;
     if (i0 + 4 <= n) {
+        // every load that does not depend on the gradient goes out first (gradient, fp16 copy, EMA): the pass is a pure
+        // stream and lives on bytes in flight; only the optimizer state of touched entries is fetched behind the test
         const uint2 graw = __ldg(reinterpret_cast<const uint2*>(grads + i0));
+        const uint2 praw = *reinterpret_cast<const uint2*>(params + i0);
+        float4 e4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (ema) e4 = *reinterpret_cast<const float4*>(ema + i0);
         const __half* gh = reinterpret_cast<const __half*>(&graw);
+        const __half* ph = reinterpret_cast<const __half*>(&praw);
         const bool matrix = i0 < h.n_matrix_params;       // n_matrix_params is a multiple of 4 (MLP layers are 16 x 64 blocks)
-        const bool any = matrix ? h.optimize_matrix : (h.optimize_non_matrix && (graw.x | graw.y) != 0u && ((graw.x & 0x7fff7fffu) | (graw.y & 0x7fff7fffu)) != 0u);
+        const bool any = matrix ? h.optimize_matrix : (h.optimize_non_matrix && ((graw.x & 0x7fff7fffu) | (graw.y & 0x7fff7fffu)) != 0u);
         __half wh[4];
+        *reinterpret_cast<uint2*>(wh) = praw;
         if (any) {
             float4 w4 = *reinterpret_cast<float4*>(master + i0), m4 = *reinterpret_cast<float4*>(m + i0), v4 = *reinterpret_cast<float4*>(v + i0);
             uint4 t4 = *reinterpret_cast<uint4*>(steps + i0);
             float* w = reinterpret_cast<float*>(&w4); float* mm = reinterpret_cast<float*>(&m4); float* vv = reinterpret_cast<float*>(&v4);
             uint32_t* tt = reinterpret_cast<uint32_t*>(&t4);
-            const uint2 praw = *reinterpret_cast<const uint2*>(params + i0);
-            const __half* ph = reinterpret_cast<const __half*>(&praw);
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
                 bool stepped;
@@ -72,12 +77,8 @@ __global__ void __launch_bounds__(256) adam_kernel(const AdamHyper h, const Adam
             *reinterpret_cast<float4*>(master + i0) = w4; *reinterpret_cast<float4*>(m + i0) = m4; *reinterpret_cast<float4*>(v + i0) = v4;
             *reinterpret_cast<uint4*>(steps + i0) = t4;
             *reinterpret_cast<uint2*>(params + i0) = *reinterpret_cast<uint2*>(wh);
-        } else if (ema) {
-            const uint2 praw = *reinterpret_cast<const uint2*>(params + i0);
-            *reinterpret_cast<uint2*>(wh) = praw;
         }
         if (ema) {
-            float4 e4 = *reinterpret_cast<float4*>(ema + i0);
             float* e = reinterpret_cast<float*>(&e4);
             __half eh[4];
 #pragma unroll
