@@ -859,9 +859,28 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_backward_kernel(uint32_t n_ra
     }
 }
 
-// ---- G lanes per ray: samples are loaded and activated in parallel (coalesced 8 B / 28 B per lane), the transmittance and
-// colour recurrences are then replayed in sample order with group shuffles, one multiply-add chain per sample — the same
-// float operations in the same order as the serial loop, so the compaction cut-off (T < 1e-4) is bit-identical.
+// ---- G lanes per ray -------------------------------------------------------------------------------------------------
+// Pass 1 keeps exactly one thing serial: the transmittance chain T *= (1 - alpha_k) with its cut-off test, replayed in
+// sample order with one group shuffle per sample — the same float operations in the same order as the reference loop, so
+// the number of samples that survive compaction is bit-identical.  Everything else is per-lane: samples are loaded and
+// activated in parallel (coalesced), lane k keeps T before its own sample (written to lb.t_before for pass 2), the ray
+// colour is a per-lane partial sum reduced once at the end, and the target / background colour work of the epilogue is
+// spread over three lanes (one per channel).  Pass 2 has no serial part at all: weight and T come from t_before, the
+// colour prefix from a group scan.  Colour sums are re-associated (float, ~1e-7 relative), counts are not.
+template <uint32_t G>
+NGP_D float group_sum(float v, uint32_t gmask) {
+#pragma unroll
+    for (uint32_t o = G / 2; o > 0; o >>= 1) v += __shfl_xor_sync(gmask, v, o);
+    return v;
+}
+template <uint32_t G>
+NGP_D float group_inclusive_scan(float v, uint32_t lane, uint32_t gmask) {
+#pragma unroll
+    for (uint32_t o = 1; o < G; o <<= 1) { const float u = __shfl_up_sync(gmask, v, o, G); if (lane >= o) v += u; }
+    return v;
+}
+NGP_D float pick3(float x, float y, float z, uint32_t c) { return c == 0 ? x : (c == 1 ? y : z); }
+
 template <uint32_t G>
 __global__ void __launch_bounds__(SCAN_BLOCK) loss_forward_group_kernel(uint32_t n_rays, Pcg32 rng, LossConfig cfg, uint32_t n_images, const ImageMeta* __restrict__ metas,
                                                                         uint32_t ray_offset, uint32_t n_rays_global, SamplerBuffers sb, LossBuffers lb) {
@@ -874,10 +893,11 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_forward_group_kernel(uint32_t
         const uint32_t numsteps = sb.numsteps[i * 2 + 0], base = sb.numsteps[i * 2 + 1];
         const float* cin = sb.coords + (size_t)base * 7;
         const __half* no = lb.network_output + (size_t)base * 4;
+        float* tb_out = lb.t_before + base;
         float T = 1.f; const float epsilon = 1e-4f;
-        V3 rgb_ray = v3(0, 0, 0);
+        V3 acc = v3(0, 0, 0);
         bool stop = false;
-        // software pipeline: the raw loads of chunk c+1 are in flight while the recurrence of chunk c is replayed
+        // software pipeline: the raw loads of chunk c+1 are in flight while the chain of chunk c is replayed
         uint2 raw_next = make_uint2(0u, 0u); float dtw_next = 0.f;
         if (lane < numsteps) { raw_next = __ldg(reinterpret_cast<const uint2*>(no + (size_t)lane * 4)); dtw_next = __ldg(cin + (size_t)lane * 7 + 3); }
         for (uint32_t c0 = 0; c0 < numsteps && !stop; c0 += G) {
@@ -894,42 +914,47 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_forward_group_kernel(uint32_t
                 alpha = 1.f - expf(-density * dt);
             }
             const uint32_t n = min(G, numsteps - c0);
+            float Tb = 0.f; uint32_t done = 0;
             for (uint32_t k = 0; k < n; ++k) {
                 if (T < epsilon) { stop = true; break; }
                 const float a = __shfl_sync(gmask, alpha, gshift + k);
-                const V3 r = v3(__shfl_sync(gmask, rgb.x, gshift + k), __shfl_sync(gmask, rgb.y, gshift + k), __shfl_sync(gmask, rgb.z, gshift + k));
-                const float weight = a * T;
-                rgb_ray = rgb_ray + weight * r;
+                if (lane == k) Tb = T;
                 T *= (1.f - a);
-                ++cn;
+                ++done;
+            }
+            cn += done;
+            if (lane < done) {
+                const float weight = alpha * Tb;
+                acc = acc + weight * rgb;
+                tb_out[idx] = Tb;
             }
         }
-        if (lane == 0) {
-            const uint32_t ig = ray_offset + sb.ray_indices[i];
-            rng.advance((int64_t)((uint64_t)ig * N_MAX_RANDOM_SAMPLES_PER_RAY));
-            const ImageMeta& m = metas[image_idx(ig, n_rays_global, n_images)];
-            float uv[2]; random_image_pos_training(rng, m.res, cfg.snap_to_pixel_centers, uv);
-            rng.advance(1);
-            V3 bg = ld3(cfg.background_color);
-            if (cfg.random_bg_color) { const float a = rng.next_float(), b = rng.next_float(), c = rng.next_float(); bg = v3(a, b, c); }
-            bg = v3(srgb_to_linear(bg.x), srgb_to_linear(bg.y), srgb_to_linear(bg.z));
-            float tex[4]; read_rgba(m, uv[0], uv[1], tex);
-            const V3 trgb = v3(tex[0], tex[1], tex[2]); const float ta = tex[3];
-            V3 target;
+        V3 rgb_ray = v3(group_sum<G>(acc.x, gmask), group_sum<G>(acc.y, gmask), group_sum<G>(acc.z, gmask));
+        // replay the sampler's RNG stream to recover pixel + background colour (:1757-1780); uniform across the group
+        const uint32_t ig = ray_offset + sb.ray_indices[i];
+        rng.advance((int64_t)((uint64_t)ig * N_MAX_RANDOM_SAMPLES_PER_RAY));
+        const ImageMeta& m = metas[image_idx(ig, n_rays_global, n_images)];
+        float uv[2]; random_image_pos_training(rng, m.res, cfg.snap_to_pixel_centers, uv);
+        rng.advance(1);
+        V3 bg3 = ld3(cfg.background_color);
+        if (cfg.random_bg_color) { const float a = rng.next_float(), b = rng.next_float(), c = rng.next_float(); bg3 = v3(a, b, c); }
+        float tex[4]; read_rgba(m, uv[0], uv[1], tex);
+        if (lane < 3) {   // one colour channel per lane: the transcendental conversions run once per warp instruction, not three times
+            float bg = srgb_to_linear(pick3(bg3.x, bg3.y, bg3.z, lane));
+            const float trgb = pick3(tex[0], tex[1], tex[2], lane), ta = tex[3];
+            float target;
             if (cfg.linear_colors) {
                 target = trgb + (1.0f - ta) * bg;
             } else {
-                bg = v3(linear_to_srgb(bg.x), linear_to_srgb(bg.y), linear_to_srgb(bg.z));
-                if (ta > 0) {
-                    const V3 q = v3(linear_to_srgb(trgb.x / ta), linear_to_srgb(trgb.y / ta), linear_to_srgb(trgb.z / ta));
-                    target = q * ta + (1.0f - ta) * bg;
-                } else target = bg;
+                bg = linear_to_srgb(bg);
+                target = ta > 0 ? linear_to_srgb(trgb / ta) * ta + (1.0f - ta) * bg : bg;
             }
-            if (cn == numsteps) rgb_ray = rgb_ray + T * bg;
+            float ray_c = pick3(rgb_ray.x, rgb_ray.y, rgb_ray.z, lane);
+            if (cn == numsteps) ray_c = ray_c + T * bg;
             float* rs = lb.ray_scratch + (size_t)i * 8;
-            rs[0] = rgb_ray.x; rs[1] = rgb_ray.y; rs[2] = rgb_ray.z; rs[3] = target.x; rs[4] = target.y; rs[5] = target.z;
-            lb.compacted_numsteps[i] = cn;
+            rs[lane] = ray_c; rs[3 + lane] = target;
         }
+        if (lane == 0) lb.compacted_numsteps[i] = cn;
     }
     uint32_t total;
     block_exclusive_scan(lane == 0 ? cn : 0u, total);
@@ -955,6 +980,7 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_backward_group_kernel(uint32_
     if (cn == 0) return;
     const float* cin = sb.coords + (size_t)base * 7;
     const __half* no = lb.network_output + (size_t)base * 4;
+    const float* tb_in = lb.t_before + base;
     const float* rs = lb.ray_scratch + (size_t)i * 8;
     const V3 rgb_ray = ld3(rs), target = ld3(rs + 3);
     const V3 ray_o = ld3(sb.rays + (size_t)i * 6);
@@ -966,30 +992,19 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_backward_group_kernel(uint32_
     const float output_l2_reg = cfg.rgb_activation == ACT_EXPONENTIAL ? 1e-4f : 0.0f;
     const float output_l1_reg_density = *mean_density < NERF_MIN_OPTICAL_THICKNESS ? 1e-4f : 0.0f;
 
-    V3 rgb_ray2 = v3(0, 0, 0); float T = 1.f;
+    V3 carry = v3(0, 0, 0);   // colour composited by the chunks before this one
     __half* gout = lb.dloss_doutput + (size_t)cbase * 4;
     float* cout = lb.coords_compacted + (size_t)cbase * 7;
-    float c_next[7] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}; uint2 raw_next = make_uint2(0u, 0u);
-    if (lane < cn) {
-#pragma unroll
-        for (int k = 0; k < 7; ++k) c_next[k] = __ldg(cin + (size_t)lane * 7 + k);
-        raw_next = __ldg(reinterpret_cast<const uint2*>(no + (size_t)lane * 4));
-    }
     for (uint32_t c0 = 0; c0 < cn; c0 += G) {
         const uint32_t j = c0 + lane;
         const bool valid = j < cn;
-        float c[7]; const uint2 raw = raw_next;
-#pragma unroll
-        for (int k = 0; k < 7; ++k) c[k] = c_next[k];
-        if (j + G < cn) {   // next chunk's loads fly while this chunk's recurrence is replayed
-#pragma unroll
-            for (int k = 0; k < 7; ++k) c_next[k] = __ldg(cin + (size_t)(j + G) * 7 + k);
-            raw_next = __ldg(reinterpret_cast<const uint2*>(no + (size_t)(j + G) * 4));
-        }
-        float o[4] = {0.f, 0.f, 0.f, 0.f}; V3 rgb = v3(0, 0, 0); float alpha = 0.f, dt = 0.f, depth = 0.f;
+        float o[4] = {0.f, 0.f, 0.f, 0.f}; V3 rgb = v3(0, 0, 0); float alpha = 0.f, dt = 0.f, depth = 0.f, Tb = 0.f;
         if (valid) {
+            float c[7];
 #pragma unroll
-            for (int k = 0; k < 7; ++k) cout[(size_t)j * 7 + k] = c[k];
+            for (int k = 0; k < 7; ++k) { c[k] = __ldg(cin + (size_t)j * 7 + k); cout[(size_t)j * 7 + k] = c[k]; }
+            const uint2 raw = __ldg(reinterpret_cast<const uint2*>(no + (size_t)j * 4));
+            Tb = tb_in[j];
             if (lb.enc_out) copy_enc_row(lb.enc_in, lb.enc_out, base + j, cbase + j, lb.enc_width);
             const V3 pos = unwarp_position(v3(c[0], c[1], c[2]), aabb);
             depth = length3(pos - ray_o);
@@ -999,24 +1014,18 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_backward_group_kernel(uint32_
             const float density = network_to_density(o[3], cfg.density_activation);
             alpha = 1.f - expf(-density * dt);
         }
-        float my_w = 0.f, my_T = 0.f; V3 my_r2 = v3(0, 0, 0);
-        const uint32_t n = min(G, cn - c0);
-        for (uint32_t k = 0; k < n; ++k) {
-            const float a = __shfl_sync(gmask, alpha, gshift + k);
-            const V3 r = v3(__shfl_sync(gmask, rgb.x, gshift + k), __shfl_sync(gmask, rgb.y, gshift + k), __shfl_sync(gmask, rgb.z, gshift + k));
-            const float weight = a * T;
-            rgb_ray2 = rgb_ray2 + weight * r;
-            T *= (1.f - a);
-            if (lane == k) { my_w = weight; my_T = T; my_r2 = rgb_ray2; }
-        }
+        const float weight = alpha * Tb, T_after = Tb * (1.f - alpha);   // the chain's own products, from its stored state
+        const V3 wr = weight * rgb;                                        // 0 on lanes past the end
+        const V3 r2 = carry + v3(group_inclusive_scan<G>(wr.x, lane, gmask), group_inclusive_scan<G>(wr.y, lane, gmask), group_inclusive_scan<G>(wr.z, lane, gmask));
+        carry = v3(__shfl_sync(gmask, r2.x, gshift + G - 1), __shfl_sync(gmask, r2.y, gshift + G - 1), __shfl_sync(gmask, r2.z, gshift + G - 1));
         if (valid) {
-            const V3 suffix = rgb_ray - my_r2;
-            const V3 dl_drgb = my_w * lg.grad;
+            const V3 suffix = rgb_ray - r2;
+            const V3 dl_drgb = weight * lg.grad;
             const float g0 = loss_scale * (dl_drgb.x * network_to_rgb_derivative(o[0], cfg.rgb_activation) + fmaxf(0.0f, output_l2_reg * o[0]));
             const float g1 = loss_scale * (dl_drgb.y * network_to_rgb_derivative(o[1], cfg.rgb_activation) + fmaxf(0.0f, output_l2_reg * o[1]));
             const float g2 = loss_scale * (dl_drgb.z * network_to_rgb_derivative(o[2], cfg.rgb_activation) + fmaxf(0.0f, output_l2_reg * o[2]));
             const float dd = network_to_density_derivative(o[3], cfg.density_activation);
-            const V3 tr = my_T * rgb - suffix;
+            const V3 tr = T_after * rgb - suffix;
             const float dl_dmlp = dd * (dt * (lg.grad.x * tr.x + lg.grad.y * tr.y + lg.grad.z * tr.z));
             const float g3 = loss_scale * dl_dmlp + (o[3] < 0.0f ? -output_l1_reg_density : 0.0f) + (o[3] > -10.0f && depth < cfg.near_distance ? 1e-4f : 0.0f);
             __half2 h[2] = {__floats2half2_rn(g0, g1), __floats2half2_rn(g2, g3)};

@@ -53,6 +53,7 @@ struct LossBuffers {
     float* loss;                    // [n_rays]
     float* ray_scratch;             // [n_rays][8]: rgb_ray(3), target(3), spare
     uint32_t* compacted_numsteps;   // [n_rays] pass-1 compacted step counts
+    float* t_before;                // [max_samples] transmittance in front of each sample that survives (pass 1 -> pass 2)
     // optional: encoder outputs of the un-compacted samples (blk8, enc_width columns) are carried along with the samples that
     // survive compaction, so the training forward pass does not gather the hash grid a second time for the same points
     const __half* enc_in; __half* enc_out; uint32_t enc_width;

@@ -315,6 +315,7 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
     lb.coords_compacted = m_coords_compacted.get<float>((size_t)target * 7); lb.loss = m_loss.get<float>(max_rays);
     lb.ray_scratch = m_ray_scratch.get<float>((size_t)max_rays * 8); lb.compacted_numsteps = m_compacted_numsteps.get<uint32_t>(max_rays);
     m_loss_sum.get<float>(4);
+    lb.t_before = m_t_before.get<float>(max_samples);
     lb.enc_width = m_nerf_net->dims.pos_width; lb.enc_out = m_nerf_net->training_encoding(target);
 
     const uint32_t max_inference = max_inference_samples(target);

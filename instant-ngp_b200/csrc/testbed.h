@@ -110,7 +110,7 @@ private:
     // sampler outputs and scratch exist twice: step N reads set N & 1 while the prefetch of step N + 1 fills the other one
     DeviceBuffer m_numsteps_all[2], m_block_steps[2], m_block_rays[2], m_ray_tmp[2], m_ray_indices[2], m_rays[2], m_numsteps[2], m_coords[2], m_counters[2],
         m_sample_scratch[2], m_sample_pool[2], m_overflow_slot[2];
-    DeviceBuffer m_mlp_out, m_dloss, m_coords_compacted, m_loss, m_ray_scratch, m_compacted_numsteps, m_loss_sum;
+    DeviceBuffer m_mlp_out, m_dloss, m_coords_compacted, m_loss, m_ray_scratch, m_compacted_numsteps, m_loss_sum, m_t_before;
     cudaStream_t m_aux_stream = nullptr; cudaEvent_t m_ev_counters = nullptr, m_ev_prefetch = nullptr, m_ev_after_mlp = nullptr;
     uint32_t* m_host_counters = nullptr;   // pinned: 4 counters + the loss sum
     bool m_prefetch_valid = false, m_all_images_u8 = false; SamplerKey m_prefetch_key{}; uint32_t m_dataset_version = 0, m_last_set = 0;
