@@ -42,15 +42,19 @@ NGP_D uint4 pack8(const float* v, bool relu) {
 }
 
 // TMEM accumulator [128 x N] (row = this thread) -> fp16 blk8 tile `dst` (C_dst columns) at column c0
-template <uint32_t N, bool RELU>
+template <uint32_t N, bool RELU, uint32_t BATCH = N>
 NGP_D void epilogue_to_smem(uint32_t tmem_row_addr, __half* dst, uint32_t C_dst, uint32_t c0, uint32_t row) {
+    // BATCH columns per tcgen05.wait::ld: the whole row at once in the backward kernel (2 CTAs per SM, latency-bound);
+    // 16 in the forward kernel (4 CTAs per SM, where the smaller register footprint and finer interleave measured faster)
 #pragma unroll
-    for (uint32_t j = 0; j < N; j += 16) {
-        float v[16];
-        tmem_ld16(tmem_row_addr + j, v);
+    for (uint32_t b = 0; b < N; b += BATCH) {
+        float v[BATCH];
+#pragma unroll
+        for (uint32_t j = 0; j < BATCH; j += 16) tmem_ld16(tmem_row_addr + b + j, v + j);
         tmem_wait_ld();
-        *reinterpret_cast<uint4*>(dst + blk8_chunk_offset(row, (c0 + j) >> 3, C_dst)) = pack8(v, RELU);
-        *reinterpret_cast<uint4*>(dst + blk8_chunk_offset(row, ((c0 + j) >> 3) + 1, C_dst)) = pack8(v + 8, RELU);
+#pragma unroll
+        for (uint32_t j = 0; j < BATCH; j += 8)
+            *reinterpret_cast<uint4*>(dst + blk8_chunk_offset(row, (c0 + b + j) >> 3, C_dst)) = pack8(v + j, RELU);
     }
 }
 
@@ -191,10 +195,10 @@ __global__ void __launch_bounds__(128) mlp_forward_kernel(const FwdParams p) {
             mbar_expect_tx(&bar_full[0], X_BYTES);
             bulk_g2s(smem + L.x0, p.enc + (size_t)next * TILE_ROWS * PW, X_BYTES, &bar_full[0]);
         }
-        epilogue_to_smem<64, true>(tmem_row, ha, MLP_WIDTH, 0, tid);
+        epilogue_to_smem<64, true, 16>(tmem_row, ha, MLP_WIDTH, 0, tid);
         for (uint32_t l = 1; l < DH; ++l) {   // hidden activations are rewritten in place: the MMAs that read them have completed
             stage.run([&] { gemm_act_wT<64>(tmem_base, HA, 0, Operand{sbase + L.wd[l], MLP_WIDTH}, MLP_WIDTH); });
-            epilogue_to_smem<64, true>(tmem_row, ha, MLP_WIDTH, 0, tid);
+            epilogue_to_smem<64, true, 16>(tmem_row, ha, MLP_WIDTH, 0, tid);
         }
         stage.run([&] { gemm_act_wT<16>(tmem_base, HA, 0, Operand{sbase + L.wd[DH], MLP_WIDTH}, MLP_WIDTH); });
         float dout[16];
@@ -213,10 +217,10 @@ __global__ void __launch_bounds__(128) mlp_forward_kernel(const FwdParams p) {
         *reinterpret_cast<uint4*>(r0 + blk8_chunk_offset(tid, 2, 32)) = pack8(sh, false);
         *reinterpret_cast<uint4*>(r0 + blk8_chunk_offset(tid, 3, 32)) = pack8(sh + 8, false);
         stage.run([&] { gemm_act_wT<64>(tmem_base, R0, 0, Operand{sbase + L.wr[0], 32}, 32); });
-        epilogue_to_smem<64, true>(tmem_row, ha, MLP_WIDTH, 0, tid);
+        epilogue_to_smem<64, true, 16>(tmem_row, ha, MLP_WIDTH, 0, tid);
         for (uint32_t l = 1; l < RH; ++l) {
             stage.run([&] { gemm_act_wT<64>(tmem_base, HA, 0, Operand{sbase + L.wr[l], MLP_WIDTH}, MLP_WIDTH); });
-            epilogue_to_smem<64, true>(tmem_row, ha, MLP_WIDTH, 0, tid);
+            epilogue_to_smem<64, true, 16>(tmem_row, ha, MLP_WIDTH, 0, tid);
         }
         stage.run([&] { gemm_act_wT<16>(tmem_base, HA, 0, Operand{sbase + L.wr[RH], MLP_WIDTH}, MLP_WIDTH); });
         float rgb[16];
@@ -285,20 +289,23 @@ struct BwdCfg {
 
 // TMEM [128 x 64] dgrad result -> ReLU-masked by the saved activation tile -> fp16 G tile (in place over the old G)
 NGP_D void epilogue_masked(uint32_t tmem_row_addr, __half* g, const __half* act, uint32_t row) {
+    float v[64];   // the whole row: every tcgen05.ld is issued before the single wait
 #pragma unroll
-    for (uint32_t j = 0; j < 64; j += 16) {
-        float v[16];
-        tmem_ld16(tmem_row_addr + j, v);
-        tmem_wait_ld();
+    for (uint32_t j = 0; j < 64; j += 16) tmem_ld16(tmem_row_addr + j, v + j);
+    uint4 a[8];    // the saved activations of the row load meanwhile
 #pragma unroll
-        for (uint32_t c = 0; c < 2; ++c) {
-            const size_t off = blk8_chunk_offset(row, (j >> 3) + c, MLP_WIDTH);
-            const uint4 a = *reinterpret_cast<const uint4*>(act + off);
-            const __half* ah = reinterpret_cast<const __half*>(&a);
+    for (uint32_t c = 0; c < 8; ++c) a[c] = *reinterpret_cast<const uint4*>(act + blk8_chunk_offset(row, c, MLP_WIDTH));
+    tmem_wait_ld();
 #pragma unroll
-            for (int i = 0; i < 8; ++i) if (!(__half2float(ah[i]) > 0.0f)) v[c * 8 + i] = 0.0f;
-            *reinterpret_cast<uint4*>(g + off) = pack8(v + c * 8, false);
-        }
+    for (uint32_t c = 0; c < 8; ++c) {
+        uint4 packed = pack8(v + c * 8, false);
+        // ReLU': keep the gradient where the activation is > 0 (fp16 compare on the packed pairs, mask applied with AND)
+        const __half2* ah = reinterpret_cast<const __half2*>(&a[c]);
+        uint32_t* pk = reinterpret_cast<uint32_t*>(&packed);
+        const __half2 zero = __float2half2_rn(0.0f);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) pk[i] &= __hgt2_mask(ah[i], zero);
+        *reinterpret_cast<uint4*>(g + blk8_chunk_offset(row, c, MLP_WIDTH)) = packed;
     }
 }
 
@@ -327,20 +334,23 @@ NGP_D void bwd_chain(StageSync& stage, uint32_t tmem_base, uint32_t tmem_row, ui
 }
 
 // flush one TMEM wgrad accumulator (M = 64 layout: row m lives in lane 32*(m/16) + m%16) to global with fp32 atomics
+NGP_D void red_add_f32x4(float* p, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
 template <uint32_t N, bool TRANSPOSED>
 NGP_D void flush_wgrad(uint32_t tmem_row, uint32_t col, float* dst, uint32_t ld, uint32_t tid) {
     const uint32_t lane = tid & 31, m = (tid >> 5) * 16 + lane;
+    float v[N];
 #pragma unroll
-    for (uint32_t j = 0; j < N; j += 16) {
-        float v[16];
-        tmem_ld16(tmem_row + col + j, v);
-        tmem_wait_ld();
-        if (lane < 16) {
+    for (uint32_t j = 0; j < N; j += 16) tmem_ld16(tmem_row + col + j, v + j);
+    tmem_wait_ld();
+    if (lane < 16) {
+        if (TRANSPOSED) {
 #pragma unroll
-            for (uint32_t i = 0; i < 16; ++i) {
-                float* p = TRANSPOSED ? dst + (size_t)(j + i) * ld + m : dst + (size_t)m * ld + (j + i);
-                atomicAdd(p, v[i]);
-            }
+            for (uint32_t i = 0; i < N; ++i) atomicAdd(dst + (size_t)i * ld + m, v[i]);
+        } else {      // row m of the gradient is contiguous: 16-byte vector reductions, a quarter of the atomic traffic
+#pragma unroll
+            for (uint32_t i = 0; i < N; i += 4) red_add_f32x4(dst + (size_t)m * ld + i, v[i], v[i + 1], v[i + 2], v[i + 3]);
         }
     }
 }
