@@ -648,30 +648,69 @@ __global__ void __launch_bounds__(SCAN_BLOCK) sampler_write_group_kernel(uint32_
     uint32_t kept_total;
     block_exclusive_scan(keep && lane == 0 ? 1u : 0u, kept_total);
     if (threadIdx.x == 0 && kept_total) atomicAdd(&b.counters[0], kept_total);
-    if (!keep) return;
-    const float* rt = b.ray_tmp + (size_t)i * 8;
-    const V3 o = ld3(rt), du = ld3(rt + 3);
-    if (lane == 0) {
-        b.ray_indices[ray_idx] = i;
-        float* r = b.rays + (size_t)ray_idx * 6;
-        r[0] = o.x; r[1] = o.y; r[2] = o.z; r[3] = du.x; r[4] = du.y; r[5] = du.z;
-        b.numsteps[ray_idx * 2 + 0] = numsteps; b.numsteps[ray_idx * 2 + 1] = base;
+    V3 o = v3(0, 0, 0), du = v3(0, 0, 1);
+    uint32_t slot = NO_SLOT;
+    if (keep) {
+        const float* rt = b.ray_tmp + (size_t)i * 8;
+        o = ld3(rt); du = ld3(rt + 3);
+        if (lane == 0) {
+            b.ray_indices[ray_idx] = i;
+            float* r = b.rays + (size_t)ray_idx * 6;
+            r[0] = o.x; r[1] = o.y; r[2] = o.z; r[3] = du.x; r[4] = du.y; r[5] = du.z;
+            b.numsteps[ray_idx * 2 + 0] = numsteps; b.numsteps[ray_idx * 2 + 1] = base;
+        }
+        if (numsteps > b.scratch_per_ray) slot = b.overflow_slot[i];
     }
-    const V3 d = normalize3(du);
-    float* coords = b.coords + (size_t)base * 7;
-    const SampleLog log{b.sample_scratch + (size_t)i * b.scratch_per_ray, b.scratch_per_ray, b.sample_pool, b.pool_slots, nullptr,
-                        numsteps > b.scratch_per_ray ? b.overflow_slot[i] : NO_SLOT};
-    if (numsteps <= b.scratch_per_ray || log.slot < b.pool_slots) {   // the counting walk left (t, dt) of every sample: no second traversal
-        const V3 wd = warp_direction(d);
-        for (uint32_t k = lane; k < numsteps; k += G) {
+    // rays whose samples the counting walk logged are expanded by sampler_expand_kernel; the few that outgrew window and pool walk again
+    const bool logged = keep && (numsteps <= b.scratch_per_ray || slot < b.pool_slots);
+    if (!keep || logged) return;
+    const float* rt = b.ray_tmp + (size_t)i * 8;
+    march_training_ray_group<G, true, FLAT>(o, normalize3(du), rt[6], rt[7], aabb, bitfield, max_mip, numsteps, b.coords + (size_t)base * 7, lane, gshift, gmask);
+}
+
+// Log -> NerfCoordinates, one thread per SAMPLE: the owning ray is found by bisection over the (ascending) base offsets of the
+// kept rays, so the work is flat — no per-ray loop whose longest ray (~10x the mean) would bound the kernel.
+__global__ void __launch_bounds__(256) sampler_expand_kernel(uint32_t max_samples, Aabb aabb, SamplerBuffers b) {
+    __shared__ __align__(16) float stage[256 * 7];
+    const uint32_t sidx = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t n_kept = b.counters[0];
+    if (n_kept == 0) return;
+    const uint32_t last = n_kept - 1;
+    bool mine = sidx < min(max_samples, b.numsteps[last * 2 + 1] + b.numsteps[last * 2 + 0]);
+    float v[7] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (mine) {
+        uint32_t lo = 0, hi = last;                       // largest r with base_r <= sidx
+        while (lo < hi) {
+            const uint32_t mid = (lo + hi + 1) >> 1;
+            if (__ldg(b.numsteps + mid * 2 + 1) <= sidx) lo = mid; else hi = mid - 1;
+        }
+        const uint32_t numsteps = b.numsteps[lo * 2 + 0], k = sidx - b.numsteps[lo * 2 + 1];
+        const uint32_t i = b.ray_indices[lo];
+        const uint32_t slot = numsteps > b.scratch_per_ray ? b.overflow_slot[i] : NO_SLOT;
+        // (rays that outgrew window and pool were written by the re-walk in sampler_write_group_kernel)
+        mine = k < numsteps && (numsteps <= b.scratch_per_ray || slot < b.pool_slots);
+        if (mine) {
+            const SampleLog log{b.sample_scratch + (size_t)i * b.scratch_per_ray, b.scratch_per_ray, b.sample_pool, b.pool_slots, nullptr, slot};
+            const float* r = b.rays + (size_t)lo * 6;
+            const V3 o = ld3(r), d = normalize3(ld3(r + 3)), wd = warp_direction(d);
             const float2 td = *log.at(k);
             const V3 wp = warp_position(ray_at(o, d, td.x), aabb);
-            float* c = coords + (size_t)k * 7;
-            c[0] = wp.x; c[1] = wp.y; c[2] = wp.z; c[3] = warp_dt(td.y); c[4] = wd.x; c[5] = wd.y; c[6] = wd.z;
+            v[0] = wp.x; v[1] = wp.y; v[2] = wp.z; v[3] = warp_dt(td.y); v[4] = wd.x; v[5] = wd.y; v[6] = wd.z;
         }
-        return;
     }
-    march_training_ray_group<G, true, FLAT>(o, d, rt[6], rt[7], aabb, bitfield, max_mip, numsteps, coords, lane, gshift, gmask);
+    // a full block owns 256 * 28 contiguous bytes of the coordinate array: staged through shared memory they leave as
+    // 16-byte vectors (448 per block) instead of seven 4-byte stores at a 28-byte stride per thread
+    if (__syncthreads_and(mine)) {
+#pragma unroll
+        for (int e = 0; e < 7; ++e) stage[threadIdx.x * 7 + e] = v[e];
+        __syncthreads();
+        float4* dst = reinterpret_cast<float4*>(b.coords + (size_t)blockIdx.x * 256 * 7);
+        for (uint32_t q = threadIdx.x; q < 448; q += 256) dst[q] = reinterpret_cast<const float4*>(stage)[q];
+    } else if (mine) {
+        float* c = b.coords + (size_t)sidx * 7;
+#pragma unroll
+        for (int e = 0; e < 7; ++e) c[e] = v[e];
+    }
 }
 
 // lanes per ray: few long rays -> a whole warp per ray; the usual tens of thousands of rays -> 8 lanes; beyond that the
@@ -708,6 +747,10 @@ void nerf_generate_training_samples(cudaStream_t s, uint32_t n_rays, Aabb aabb, 
     else if (G == 8) NGP_SAMPLER_WRITE(8);
     else if (G == 4) NGP_SAMPLER_WRITE(4);
     else NGP_SAMPLER_WRITE(2);
+    if (G != 1) {
+        NGP_POST_LAUNCH();
+        sampler_expand_kernel<<<div_round_up(max_samples, 256), 256, 0, s>>>(max_samples, aabb, b);
+    }
     NGP_POST_LAUNCH();
 }
 
