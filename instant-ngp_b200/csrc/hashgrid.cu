@@ -179,7 +179,15 @@ __global__ void __launch_bounds__(256) grid_forward_kernel(const GridLayout g, c
 }
 
 // vector reductions into the fp16 gradient table (RED.E.ADD.F16x2; one instruction per table entry)
-NGP_D void red_add_h2(__half* p, float a, float b) { atomicAdd(reinterpret_cast<__half2*>(p), __floats2half2_rn(a, b)); }
+// (explicit .global: atomicAdd on a generic pointer compiles to an address-space test + shared-memory CAS loop + ATOM)
+NGP_D void red_add_h2(__half* p, float a, float b) {
+    __half2 v = __floats2half2_rn(a, b);
+    asm volatile("red.global.add.noftz.f16x2 [%0], %1;" ::"l"(p), "r"(*reinterpret_cast<uint32_t*>(&v)) : "memory");
+}
+NGP_D void red_add_h1(__half* p, float a) {
+    __half v = __float2half_rn(a);
+    asm volatile("red.global.add.noftz.f16 [%0], %1;" ::"l"(p), "h"(*reinterpret_cast<unsigned short*>(&v)) : "memory");
+}
 NGP_D void red_add_h4(__half* p, float a, float b, float c, float d) {
     __half2 lo = __floats2half2_rn(a, b), hi = __floats2half2_rn(c, d);
     asm volatile("red.global.add.noftz.v2.f16x2 [%0], {%1, %2};" ::"l"(p), "r"(*reinterpret_cast<uint32_t*>(&lo)), "r"(*reinterpret_cast<uint32_t*>(&hi)) : "memory");
@@ -192,7 +200,7 @@ NGP_D void red_add_h8(__half* p, float a, float b, float c, float d, float e, fl
 }
 template <uint32_t F>
 NGP_D void red_add_entry(__half* p, float w, const float* d) {
-    if (F == 1) atomicAdd(p, __float2half_rn(w * d[0]));
+    if (F == 1) red_add_h1(p, w * d[0]);
     else if (F == 2) red_add_h2(p, w * d[0], w * d[1 % F]);
     else if (F == 4) red_add_h4(p, w * d[0], w * d[1 % F], w * d[2 % F], w * d[3 % F]);
     else { red_add_h4(p, w * d[0], w * d[1 % F], w * d[2 % F], w * d[3 % F]); red_add_h4(p + 4, w * d[4 % F], w * d[5 % F], w * d[6 % F], w * d[7 % F]); }
