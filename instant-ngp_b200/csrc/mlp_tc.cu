@@ -31,14 +31,13 @@ NGP_D void load_weights_blk8(__half* dst, const __half* __restrict__ src, uint32
 }
 
 NGP_D uint4 pack8(const float* v, bool relu) {
-    __half2 h[4];
+    uint32_t h[4];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        float a = v[2 * i], b = v[2 * i + 1];
-        if (relu) { a = fmaxf(a, 0.0f); b = fmaxf(b, 0.0f); }
-        h[i] = __floats2half2_rn(a, b);
+    for (int i = 0; i < 4; ++i) {   // (lo, hi) = (v[2i], v[2i+1]); ReLU rides on the conversion (cvt.rn.relu.f16x2.f32)
+        if (relu) asm("cvt.rn.relu.f16x2.f32 %0, %1, %2;" : "=r"(h[i]) : "f"(v[2 * i + 1]), "f"(v[2 * i]));
+        else asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(h[i]) : "f"(v[2 * i + 1]), "f"(v[2 * i]));
     }
-    return *reinterpret_cast<uint4*>(h);
+    return make_uint4(h[0], h[1], h[2], h[3]);
 }
 
 // TMEM accumulator [128 x N] (row = this thread) -> fp16 blk8 tile `dst` (C_dst columns) at column c0
