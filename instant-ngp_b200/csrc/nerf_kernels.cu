@@ -217,6 +217,44 @@ void nerf_update_bitfield(cudaStream_t s, const float* grid, uint32_t n_cascades
 }
 
 
+// ---- dilated coarse occupancy (ray classification) -----------------------------------------------------------------
+constexpr uint32_t COARSE_RES = 32, COARSE_MIP = 2;   // 32^3 cells of 4^3 fine cells each = mip 2 of the bitfield pyramid
+__global__ void coarse_occupancy_kernel(const uint8_t* __restrict__ bitfield, uint32_t* __restrict__ coarse) {
+    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;            // x fastest
+    const int x = c % COARSE_RES, y = (c / COARSE_RES) % COARSE_RES, z = c / (COARSE_RES * COARSE_RES);
+    bool occ = false;
+    for (int dz = -1; dz <= 1; ++dz) for (int dy = -1; dy <= 1; ++dy) for (int dx = -1; dx <= 1; ++dx) {
+        const int xx = x + dx, yy = y + dy, zz = z + dz;
+        if (xx < 0 || yy < 0 || zz < 0 || xx >= (int)COARSE_RES || yy >= (int)COARSE_RES || zz >= (int)COARSE_RES) continue;
+        const V3 centre = v3(((float)xx + 0.5f) / COARSE_RES, ((float)yy + 0.5f) / COARSE_RES, ((float)zz + 0.5f) / COARSE_RES);
+        occ = occ || density_grid_occupied_at(centre, bitfield, COARSE_MIP);
+    }
+    const uint32_t word = __ballot_sync(0xffffffffu, occ);
+    if ((threadIdx.x & 31u) == 0) coarse[c >> 5] = word;
+}
+void nerf_build_coarse_occupancy(cudaStream_t s, const uint8_t* bitfield, uint32_t* coarse) {
+    coarse_occupancy_kernel<<<COARSE_RES * COARSE_RES * COARSE_RES / 256, 256, 0, s>>>(bitfield, coarse);
+    NGP_POST_LAUNCH();
+}
+// Conservative test "can the exact walk of this ray ever stand in an occupied cell?": the ray is sampled every 0.05 inside
+// the aabb (any point of it is within 0.025 of a sample), the coarse cells are 1/32 = 0.03125 wide and dilated by one cell,
+// so a walk position in an occupied fine cell always has a sample in a set coarse cell.  false => the walk yields 0 samples.
+NGP_D bool ray_touches_coarse(const uint32_t* __restrict__ coarse, V3 o, V3 d, float tmin, float tmax, uint32_t part, uint32_t n_parts) {
+    if (!(tmax >= tmin)) return true;    // degenerate interval / NaN: let the walk decide
+    const float t0 = tmin - 0.01f, t1 = tmax + 0.01f;
+    const uint32_t n = (uint32_t)fminf(ceilf((t1 - t0) * 20.0f), 64.0f) + 1u;
+    if (n > 64u) return true;
+    for (uint32_t k = part; k < n; k += n_parts) {     // the samples are dealt out to the n_parts lanes that share the ray
+        const float t = fminf(t0 + (float)k * 0.05f, t1);
+        const V3 p = ray_at(o, d, t);
+        const uint32_t x = (uint32_t)clampi((int)floorf(p.x * COARSE_RES), 0, COARSE_RES - 1), y = (uint32_t)clampi((int)floorf(p.y * COARSE_RES), 0, COARSE_RES - 1),
+                       z = (uint32_t)clampi((int)floorf(p.z * COARSE_RES), 0, COARSE_RES - 1);
+        const uint32_t c = (z * COARSE_RES + y) * COARSE_RES + x;
+        if ((__ldg(coarse + (c >> 5)) >> (c & 31u)) & 1u) return true;
+    }
+    return false;
+}
+
 // =================================================================================================================
 // Training sampler: generate_training_samples_nerf (testbed_nerf.cu:1382-1658)
 //   pass 1 (count)  : pick image + pixel, build the ray, clip to the aabb, march the occupancy bitfield counting samples
@@ -590,46 +628,68 @@ NGP_D uint32_t march_training_ray_group(V3 o, V3 d, float startt, float cone, co
     return j;
 }
 
-template <uint32_t G, bool FLAT, uint32_t K>
-__global__ void __launch_bounds__(SCAN_BLOCK) sampler_count_group_kernel(uint32_t n_rays, Aabb aabb, Pcg32 rng, uint32_t n_images, const ImageMeta* __restrict__ metas,
-                                                                         const uint8_t* __restrict__ bitfield, uint32_t max_mip, bool snap, float cone_angle_constant,
-                                                                         uint32_t ray_offset, uint32_t n_rays_global, SamplerBuffers b) {
-    constexpr uint32_t RPB = SCAN_BLOCK / G;
-    const uint32_t lane = threadIdx.x % G, gshift = (threadIdx.x & 31u) / G * G;
-    const uint32_t gmask = G == 32 ? 0xffffffffu : (((1u << G) - 1u) << gshift);
-    const uint32_t i = blockIdx.x * RPB + threadIdx.x / G;
-    uint32_t numsteps = 0;
-    if (i < n_rays) {   // group-uniform: every lane of the group builds the same ray
+// Pass 0 of the group marchers, one thread per ray: pick image + pixel, build the ray, clip it to the aabb, and decide whether
+// it has to be walked at all.  About two thirds of the training rays never meet an occupied cell; the walk would still
+// follow their exact t chain through ~160 empty voxels.  Rays that fail the conservative coarse test have 0 samples by
+// construction and are not walked; the others are appended to the candidate list (order irrelevant: results are per ray).
+__global__ void __launch_bounds__(128) sampler_classify_kernel(uint32_t n_rays, Aabb aabb, Pcg32 rng, uint32_t n_images, const ImageMeta* __restrict__ metas,
+                                                               bool snap, float cone_angle_constant, uint32_t ray_offset, uint32_t n_rays_global, uint32_t rays_per_block,
+                                                               SamplerBuffers b) {
+    constexpr uint32_t Q = 4;                                            // lanes per ray: the coarse test is split four ways
+    const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, i = tid / Q, part = tid % Q;
+    if (tid < (n_rays + rays_per_block - 1) / rays_per_block) { b.block_steps[tid] = 0; b.block_rays[tid] = 0; }   // totals are accumulated by the walk
+    bool candidate = false;
+    if (i < n_rays) {   // the Q lanes of a ray build it redundantly (uniform), lane 0 stores
         const uint32_t ig = ray_offset + i;
         const uint32_t img = image_idx(ig, n_rays_global, n_images);
         const ImageMeta& m = metas[img];
         rng.advance((int64_t)((uint64_t)ig * N_MAX_RANDOM_SAMPLES_PER_RAY));
         float uv[2]; random_image_pos_training(rng, m.res, snap, uv);
         float texel[4]; read_rgba(m, uv[0], uv[1], texel);
-        if (texel[0] >= 0.0f) {
-            (void)rng.next_float();
+        if (texel[0] >= 0.0f) {   // negative = masked-away pixel (:1430-1435)
+            (void)rng.next_float();   // motionblur_time (:1440)
             V3 o, du; uv_to_ray(m.xform, m.res, m.focal_length, m.principal_point, m.lens_mode, m.lens_params, uv[0], uv[1], o, du);
             if (du.x == 0.f && du.y == 0.f && du.z == 0.f) { o = v3(m.xform[9], m.xform[10], m.xform[11]); du = v3(m.xform[6], m.xform[7], m.xform[8]); }
             const V3 d = normalize3(du);
             float tmin, tmax; aabb_ray_intersect(aabb, o, d, tmin, tmax);
-            const float cone = cone_angle_constant;
+            const float cone = cone_angle_constant;   // calc_cone_angle (:114-122)
             tmin = fmaxf(tmin, 0.0f);
-            const float startt = advance_n_steps(tmin, cone, rng.next_float());
-            SampleLog log{b.sample_scratch + (size_t)i * b.scratch_per_ray, b.scratch_per_ray, b.sample_pool, b.pool_slots, &b.counters[3], NO_SLOT};
-            numsteps = march_training_ray_group<G, false, FLAT, K>(o, d, startt, cone, aabb, bitfield, max_mip, NERF_STEPS, nullptr, lane, gshift, gmask, &log);
-            if (lane == 0) b.overflow_slot[i] = log.slot;
-            if (lane == 0) {
+            if (part == 0) {
+                const float startt = advance_n_steps(tmin, cone, rng.next_float());
                 float* rt = b.ray_tmp + (size_t)i * 8;
                 rt[0] = o.x; rt[1] = o.y; rt[2] = o.z; rt[3] = du.x; rt[4] = du.y; rt[5] = du.z; rt[6] = startt; rt[7] = cone;
             }
+            candidate = b.coarse == nullptr || ray_touches_coarse(b.coarse, o, d, tmin, tmax, part, Q);
         }
-        if (lane == 0) b.numsteps_all[i] = numsteps;
+        if (part == 0) { b.numsteps_all[i] = 0; b.overflow_slot[i] = NO_SLOT; }
     }
-    const uint32_t v = lane == 0 ? numsteps : 0u;
-    uint32_t total_steps, total_rays;
-    block_exclusive_scan(v, total_steps);
-    block_exclusive_scan(v > 0 ? 1u : 0u, total_rays);
-    if (threadIdx.x == 0) { b.block_steps[blockIdx.x] = total_steps; b.block_rays[blockIdx.x] = total_rays; }
+    // a ray is a candidate if any of its lanes found a set cell; warp-aggregated append by the first lane of each ray
+    const uint32_t any = __ballot_sync(0xffffffffu, candidate), lane = threadIdx.x & 31u;
+    const bool mine = part == 0 && ((any >> (lane & ~(Q - 1u))) & ((1u << Q) - 1u)) != 0u;
+    const uint32_t mask = __ballot_sync(0xffffffffu, mine);
+    uint32_t base = 0;
+    if (lane == 0 && mask) base = atomicAdd(&b.counters[4], (uint32_t)__popc(mask));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (mine) b.cand_list[base + __popc(mask & ((1u << lane) - 1u))] = i;
+}
+
+template <uint32_t G, bool FLAT, uint32_t K>
+__global__ void __launch_bounds__(SCAN_BLOCK) sampler_count_group_kernel(uint32_t n_rays, Aabb aabb, const uint8_t* __restrict__ bitfield, uint32_t max_mip, SamplerBuffers b) {
+    constexpr uint32_t RPB = SCAN_BLOCK / G;
+    const uint32_t lane = threadIdx.x % G, gshift = (threadIdx.x & 31u) / G * G;
+    const uint32_t gmask = G == 32 ? 0xffffffffu : (((1u << G) - 1u) << gshift);
+    const uint32_t c = blockIdx.x * RPB + threadIdx.x / G;
+    if (c >= b.counters[4]) return;   // group-uniform
+    const uint32_t i = b.cand_list[c];
+    const float* rt = b.ray_tmp + (size_t)i * 8;
+    const V3 o = ld3(rt), du = ld3(rt + 3);
+    const float startt = rt[6], cone = rt[7];
+    SampleLog log{b.sample_scratch + (size_t)i * b.scratch_per_ray, b.scratch_per_ray, b.sample_pool, b.pool_slots, &b.counters[3], NO_SLOT};
+    const uint32_t numsteps = march_training_ray_group<G, false, FLAT, K>(o, normalize3(du), startt, cone, aabb, bitfield, max_mip, NERF_STEPS, nullptr, lane, gshift, gmask, &log);
+    if (lane == 0) {
+        b.overflow_slot[i] = log.slot; b.numsteps_all[i] = numsteps;
+        if (numsteps) { atomicAdd(&b.block_steps[i / RPB], numsteps); atomicAdd(&b.block_rays[i / RPB], 1u); }   // per-block totals of the ray-order scan
+    }
 }
 
 template <uint32_t G, bool FLAT>
@@ -728,10 +788,14 @@ void nerf_generate_training_samples(cudaStream_t s, uint32_t n_rays, Aabb aabb, 
     if (const char* e = getenv("NGP_SAMPLER_K")) K = (uint32_t)atoi(e);
     const bool flat = cone_angle_constant <= 1e-5f && max_mip == 0;
     const uint32_t blocks = div_round_up(n_rays, SCAN_BLOCK / G);
-#define NGP_SAMPLER_COUNT(GG, FF, KK) sampler_count_group_kernel<GG, FF, KK><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, rng, n_images, metas, bitfield, max_mip, snap, cone_angle_constant, ray_offset, n_rays_global, b)
+#define NGP_SAMPLER_COUNT(GG, FF, KK) sampler_count_group_kernel<GG, FF, KK><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, bitfield, max_mip, b)
 #define NGP_SAMPLER_COUNT_F(GG, KK) do { if (flat) NGP_SAMPLER_COUNT(GG, true, KK); else NGP_SAMPLER_COUNT(GG, false, KK); } while (0)
 #define NGP_SAMPLER_WRITE(GG) do { if (flat) sampler_write_group_kernel<GG, true><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, max_samples, bitfield, max_mip, b); \
                                    else sampler_write_group_kernel<GG, false><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, max_samples, bitfield, max_mip, b); } while (0)
+    if (G != 1) {
+        sampler_classify_kernel<<<div_round_up(n_rays * 4, 128), 128, 0, s>>>(n_rays, aabb, rng, n_images, metas, snap, cone_angle_constant, ray_offset, n_rays_global, SCAN_BLOCK / G, b);
+        NGP_POST_LAUNCH();
+    }
     if (G == 1) { if (flat) sampler_count_kernel<true><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, rng, n_images, metas, bitfield, max_mip, snap, cone_angle_constant, ray_offset, n_rays_global, b);
                   else sampler_count_kernel<false><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, rng, n_images, metas, bitfield, max_mip, snap, cone_angle_constant, ray_offset, n_rays_global, b); }
     else if (G == 32) NGP_SAMPLER_COUNT_F(32, 1);

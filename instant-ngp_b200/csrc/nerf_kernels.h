@@ -13,6 +13,8 @@ void nerf_splat_grid_samples(cudaStream_t s, uint32_t n, const uint32_t* indices
 void nerf_ema_grid(cudaStream_t s, uint32_t n_elements, float decay, float* grid, const float* grid_tmp);
 // mean over cascade 0 (deterministic two-stage reduction) -> *mean_dev ; bitfield + 7 OR-pooled mips
 void nerf_update_bitfield(cudaStream_t s, const float* grid, uint32_t n_cascades, uint8_t* bitfield, float* mean_dev, float* partials /* [1024] */);
+// 32^3 coarse cells of the unit cube, bit set if the cell or one of its 26 neighbours holds an occupied fine cell (mip 2 of the bitfield)
+void nerf_build_coarse_occupancy(cudaStream_t s, const uint8_t* bitfield, uint32_t* coarse /* [1024] */);
 
 // ---- training sampler (testbed_nerf.cu:1382-1658), deterministic ray-order compaction ----
 struct SamplerBuffers {
@@ -26,10 +28,13 @@ struct SamplerBuffers {
     float* rays;                // [n_rays][6] unnormalised o,d
     uint32_t* numsteps;         // [n_rays][2] (numsteps, base)
     float* coords;              // [max_samples][7]
-    uint32_t* counters;         // [0] ray_counter, [1] numsteps_counter (total, may exceed max_samples), [2] compacted counter, [3] pool slots taken
+    uint32_t* counters;         // [8]: [0] ray_counter, [1] numsteps_counter (total, may exceed max_samples), [2] compacted counter, [3] pool slots taken, [4] candidate rays
     float2* sample_scratch;     // [n_rays][scratch_per_ray] (t, dt) of the samples found by the counting walk
     uint32_t scratch_per_ray;   // window per ray; rays that outgrow it continue in a pool slot (NERF_STEPS entries each)
     float2* sample_pool; uint32_t pool_slots; uint32_t* overflow_slot;   // [pool_slots][NERF_STEPS]; [n_rays] slot of ray i or NO_SLOT; counters[3] = slots taken
+    // ray classification (group marchers): rays that cannot touch an occupied cell are never walked
+    const uint32_t* coarse;     // 32^3-bit dilated coarse occupancy of the unit cube (nerf_build_coarse_occupancy) or nullptr: every ray is walked
+    uint32_t* cand_list;        // [n_rays] indices of the rays to walk; counters[4] = how many
     uint32_t lanes_per_ray;     // 0: choose from n_rays (nerf_sampler_lanes_per_ray); 1 / 4 / 8 / 32: forced (tests compare the variants)
 };
 uint32_t nerf_sampler_lanes_per_ray(uint32_t n_rays);

@@ -155,6 +155,7 @@ void Testbed::update_density_grid_nerf(cudaStream_t s, float decay, uint32_t n_u
     nerf_ema_grid(s, n_elements, decay, grid, tmp);
     ++m_density_grid_ema_step;
     nerf_update_bitfield(s, grid, n_cascades, m_bitfield.as<uint8_t>(), m_mean.as<float>(), m_partials.as<float>());
+    nerf_build_coarse_occupancy(s, m_bitfield.as<uint8_t>(), m_coarse.get<uint32_t>(1024));
 }
 
 void Testbed::training_prep_nerf(cudaStream_t s) {
@@ -252,7 +253,11 @@ SamplerBuffers Testbed::sampler_buffers(cudaStream_t s, uint32_t set, uint32_t t
     const bool fresh_coords = m_coords[set].bytes < (size_t)max_samples * 7 * 4;
     sb.coords = m_coords[set].get<float>((size_t)max_samples * 7);
     if (fresh_coords) NGP_CUDA_CHECK(cudaMemsetAsync(sb.coords, 0, (size_t)max_samples * 7 * 4, s));   // stale rows are fed to the network: keep them finite
-    sb.counters = m_counters[set].get<uint32_t>(4);
+    sb.counters = m_counters[set].get<uint32_t>(8);
+    sb.cand_list = m_cand_list[set].get<uint32_t>(max_rays);
+    // classification needs the unit-cube scene (one cascade); otherwise every ray is walked
+    const bool unit = m_max_cascade == 0 && aabb.min[0] == 0.f && aabb.min[1] == 0.f && aabb.min[2] == 0.f && aabb.max[0] == 1.f && aabb.max[1] == 1.f && aabb.max[2] == 1.f;
+    sb.coarse = unit && m_coarse.ptr ? m_coarse.as<uint32_t>() : nullptr;
     sb.lanes_per_ray = sampler_lanes_per_ray;
     sb.sample_scratch = m_sample_scratch[set].get<float2>(max_samples);
     sb.scratch_per_ray = std::min<uint32_t>(NERF_STEPS, max_samples / n_rays);
@@ -269,7 +274,7 @@ uint32_t Testbed::max_inference_samples(uint32_t target) {
 
 // prepare_for_training_steps (:3569-3581) + generate_training_samples_nerf (:1382-1658)
 void Testbed::launch_sampler(cudaStream_t s, const SamplerKey& key, const SamplerBuffers& sb) {
-    NGP_CUDA_CHECK(cudaMemsetAsync(sb.counters, 0, 16, s));
+    NGP_CUDA_CHECK(cudaMemsetAsync(sb.counters, 0, 32, s));
     nerf_generate_training_samples(s, key.n_rays, aabb, key.max_inference, 0, m_rng, m_n_images, m_metas.as<ImageMeta>(), m_bitfield.as<uint8_t>(), m_max_cascade,
                                    snap_to_pixel_centers, cone_angle_constant, m_rank * key.n_rays, m_world * key.n_rays, sb);
 }

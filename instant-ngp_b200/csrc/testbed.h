@@ -109,7 +109,8 @@ private:
     // per-step scratch
     // sampler outputs and scratch exist twice: step N reads set N & 1 while the prefetch of step N + 1 fills the other one
     DeviceBuffer m_numsteps_all[2], m_block_steps[2], m_block_rays[2], m_ray_tmp[2], m_ray_indices[2], m_rays[2], m_numsteps[2], m_coords[2], m_counters[2],
-        m_sample_scratch[2], m_sample_pool[2], m_overflow_slot[2];
+        m_sample_scratch[2], m_sample_pool[2], m_overflow_slot[2], m_cand_list[2];
+    DeviceBuffer m_coarse;   // dilated 16^3 coarse occupancy (ray classification), rebuilt with the bitfield
     DeviceBuffer m_mlp_out, m_dloss, m_coords_compacted, m_loss, m_ray_scratch, m_compacted_numsteps, m_loss_sum, m_t_before;
     cudaStream_t m_aux_stream = nullptr; cudaEvent_t m_ev_counters = nullptr, m_ev_prefetch = nullptr, m_ev_after_mlp = nullptr;
     uint32_t* m_host_counters = nullptr;   // pinned: 4 counters + the loss sum
