@@ -113,12 +113,12 @@ void NerfNetwork::forward_backward(cudaStream_t s, const __half* params, const f
 }
 
 void NerfNetwork::forward_backward_encoded(cudaStream_t s, const __half* params, const float* coords, uint32_t n, const __half* dL_dout, __half* grads,
-                                           cudaEvent_t after_mlp) {
+                                           cudaEvent_t after_mlp, bool grid_grads_clean) {
     const __half* enc = enc_train_buf.as<__half>();
     __half* denc = denc_buf.get<__half>((size_t)n * dims.pos_width);
     float* wg = wgrad_buf.get<float>(n_matrix_params);
     NGP_CUDA_CHECK(cudaMemsetAsync(wg, 0, n_matrix_params * sizeof(float), s));
-    NGP_CUDA_CHECK(cudaMemsetAsync(grads + off_grid, 0, grid.n_params * sizeof(__half), s));
+    if (!grid_grads_clean) NGP_CUDA_CHECK(cudaMemsetAsync(grads + off_grid, 0, grid.n_params * sizeof(__half), s));
     nerf_mlp_backward(s, dims, params + off_density, params + off_rgb, enc, coords, n, dL_dout, denc, wg);
     cast_f32_to_half(s, wg, grads, n_matrix_params);
     if (after_mlp) NGP_CUDA_CHECK(cudaEventRecord(after_mlp, s));
@@ -213,6 +213,7 @@ void Trainer::optimizer_step(cudaStream_t s, float loss_scale) {
     h.loss_scale = loss_scale; h.n_matrix_params = n_matrix_params;
     h.optimize_matrix = opt.optimize_matrix; h.optimize_non_matrix = opt.optimize_non_matrix;
     h.ema_decay = opt.ema_decay; h.ema_step = opt.step_count + 1;
+    h.clear_consumed_grads = 1; grid_grads_clean = true;
     adam_step(s, h, n_params, master, params, grads, m, v, steps, ema, ema ? inference_params : nullptr);
     ++opt.step_count;
     const uint32_t sc = opt.step_count;

@@ -47,7 +47,7 @@ struct NerfNetwork {
     void forward_backward(cudaStream_t s, const __half* params, const float* coords, uint32_t n, const __half* dL_dout, __half* grads);
     // same, with the encoder outputs of the n samples already known (blk8 rows in enc_train_buf, carried over from inference())
     void forward_backward_encoded(cudaStream_t s, const __half* params, const float* coords, uint32_t n, const __half* dL_dout, __half* grads,
-                                  cudaEvent_t after_mlp = nullptr);   // recorded between the MLP and the hash-grid backward kernels
+                                  cudaEvent_t after_mlp = nullptr, bool grid_grads_clean = false);   // recorded between the MLP and the hash-grid backward kernels
     const __half* last_inference_encoding() const { return enc_buf.as<__half>(); }
     __half* training_encoding(uint32_t n) { return enc_train_buf.get<__half>((size_t)n * dims.pos_width); }
 };
@@ -86,6 +86,7 @@ struct Trainer {
     Trainer(const Trainer&) = delete;
     void params_from_master(cudaStream_t s);             // fp16 copies after initialize_params
     void optimizer_step(cudaStream_t s, float loss_scale);
+    bool grid_grads_clean = false;   // the hash-table part of `grads` is all zero (left so by the last optimizer step)
 };
 
 }  // namespace ngp

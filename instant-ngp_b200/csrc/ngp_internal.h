@@ -87,6 +87,8 @@ struct AdamHyper {
     int optimize_matrix, optimize_non_matrix;
     float ema_decay;      // 0: no EMA
     uint32_t ema_step;    // 1-based step for debiasing
+    int clear_consumed_grads;   // write zeros back over the non-zero hash-table gradients once read: the table is then clean for the
+                                // next backward pass, which can skip its 24 MB memset (Trainer; the C ABI entry leaves gradients alone)
 };
 // grads_f32_matrix (optional): fp32 gradients of the first n_matrix params (MLP wgrad staging); if null, fp16 grads used
 void adam_step(cudaStream_t s, const AdamHyper& h, uint64_t n, float* master, __half* params, const __half* grads,

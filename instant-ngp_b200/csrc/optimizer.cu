@@ -60,7 +60,9 @@ __global__ void __launch_bounds__(256) adam_kernel(const AdamHyper h, const Adam
         const __half* gh = reinterpret_cast<const __half*>(&graw);
         const __half* ph = reinterpret_cast<const __half*>(&praw);
         const bool matrix = i0 < h.n_matrix_params;       // n_matrix_params is a multiple of 4 (MLP layers are 16 x 64 blocks)
-        const bool any = matrix ? h.optimize_matrix : (h.optimize_non_matrix && ((graw.x & 0x7fff7fffu) | (graw.y & 0x7fff7fffu)) != 0u);
+        const bool nonzero = ((graw.x & 0x7fff7fffu) | (graw.y & 0x7fff7fffu)) != 0u;
+        const bool any = matrix ? h.optimize_matrix : (h.optimize_non_matrix && nonzero);
+        if (h.clear_consumed_grads && !matrix && nonzero) *reinterpret_cast<uint2*>(const_cast<__half*>(grads) + i0) = make_uint2(0u, 0u);
         __half wh[4];
         *reinterpret_cast<uint2*>(wh) = praw;
         if (any) {
@@ -95,6 +97,7 @@ __global__ void __launch_bounds__(256) adam_kernel(const AdamHyper h, const Adam
         const bool matrix = i < h.n_matrix_params;
         float w = master[i], mm = m[i], vv = v[i]; uint32_t t = steps[i]; bool stepped;
         adam_one(h, c, matrix, __half2float(grads[i]), w, mm, vv, t, stepped);
+        if (h.clear_consumed_grads && !matrix) const_cast<__half*>(grads)[i] = __float2half_rn(0.0f);
         __half wh = params[i];
         if (stepped) { master[i] = w; m[i] = mm; v[i] = vv; steps[i] = t; wh = __float2half_rn(w); params[i] = wh; }
         if (ema) {

@@ -348,7 +348,8 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
     NGP_CUDA_CHECK(cudaEventRecord(m_ev_counters, s));
     nerf_fill_rollover(s, target, &sb.counters[2], lb.dloss_doutput, lb.coords_compacted, lb.enc_out, lb.enc_width);   // :4061-4069
     // forward(compacted) + backward(EGradientMode::Overwrite) (:4077-4078)
-    m_nerf_net->forward_backward_encoded(s, m_trainer->params, lb.coords_compacted, target, lb.dloss_doutput, m_trainer->grads, m_ev_after_mlp);
+    m_nerf_net->forward_backward_encoded(s, m_trainer->params, lb.coords_compacted, target, lb.dloss_doutput, m_trainer->grads, m_ev_after_mlp, m_trainer->grid_grads_clean);
+    m_trainer->grid_grads_clean = false;
     m_rng.advance();   // :4127
 }
 
