@@ -34,6 +34,16 @@ def main():
             cold = timeit(fn, flush=flush); warm = timeit(fn)
             res[f"grid_{name}_{tag}"] = {"ms_cold_med": cold[0], "ms_warm_med": warm[0], "ms_warm_min": warm[1],
                                         "Gpoints_s_warm": N / warm[0] / 1e6, "GBs_alg_warm": N * 588 / warm[0] / 1e6}
+    # denominator for "fraction of L2 gather bandwidth" (SURVEY 8d): random 4-byte gathers over a 24.4 MB (L2-resident) table,
+    # torch.take as a neutral gather kernel; 1 sector (32 B) per gather
+    tab = torch.randint(0, 1 << 30, (6098120,), dtype=torch.int32, device="cuda")
+    idx = torch.randint(0, tab.numel(), (1 << 26,), dtype=torch.int64, device="cuda")
+    t = timeit(lambda: torch.take(tab, idx), iters=10)
+    res["l2_random_gather_4B"] = {"ms_med": t[0], "Ggathers_s": idx.numel() / t[0] / 1e6, "sector_GBs": idx.numel() * 32 / t[0] / 1e6, "table_MB": tab.numel() * 4 / 1e6}
+    for k in list(res):
+        if k.startswith("grid_") and "T19" in k:
+            res[k]["Ggathers_s_warm"] = N * 128 / res[k]["ms_warm_med"] / 1e6
+            res[k]["frac_of_l2_gather_rate"] = res[k]["Ggathers_s_warm"] / res["l2_random_gather_4B"]["Ggathers_s"]
     cfg = {"encoding": {"otype": "HashGrid", "n_levels": 16, "n_features_per_level": 2, "log2_hashmap_size": 19, "base_resolution": 16, "per_level_scale": 1.3819},
            "network": {"otype": "FullyFusedMLP", "n_neurons": 64, "n_hidden_layers": 1}, "rgb_network": {"otype": "FullyFusedMLP", "n_neurons": 64, "n_hidden_layers": 2}}
     net = ops.NerfNetwork(cfg)
