@@ -152,6 +152,10 @@ int ngp_testbed_train(ngp_testbed_t t, void* stream, uint32_t batch_size);      
  * (sum) the fp16 gradient buffer; measured_* = 0 keeps the local sample counts for the rays-per-batch control law. */
 int ngp_testbed_train_begin(ngp_testbed_t t, void* stream, uint32_t batch_size);
 int ngp_testbed_train_end(ngp_testbed_t t, void* stream, uint32_t measured_batch_size, uint32_t measured_batch_size_before_compaction);
+/* local (measured, measured_before_compaction) of the step begun by train_begin; returns as soon as the loss kernel has
+ * run, while the backward pass is still in flight, so that the host can exchange the counts under it
+ * (NerfCounters, testbed.h:433-447) */
+int ngp_testbed_pending_counters(ngp_testbed_t t, uint32_t* measured_batch_size, uint32_t* measured_batch_size_before_compaction);
 int ngp_testbed_set_shard(ngp_testbed_t t, uint32_t rank, uint32_t world_size);
 int ngp_testbed_stats(ngp_testbed_t t, ngp_train_stats* out);
 uint64_t ngp_testbed_n_params(ngp_testbed_t t);                                         /* Testbed::n_params python_api.cu:440 */

@@ -219,6 +219,11 @@ int ngp_testbed_train_end(ngp_testbed_t t, void* stream, uint32_t measured, uint
     t->tb.train_end(S(stream), measured, measured_before);
     NGP_API_END
 }
+int ngp_testbed_pending_counters(ngp_testbed_t t, uint32_t* measured, uint32_t* measured_before) {
+    NGP_API_BEGIN require_device(); NGP_CHECK(t && measured && measured_before, "null argument");
+    t->tb.pending_counters(measured, measured_before);
+    NGP_API_END
+}
 int ngp_testbed_set_shard(ngp_testbed_t t, uint32_t rank, uint32_t world) {
     NGP_API_BEGIN NGP_CHECK(t && world >= 1 && rank < world, "bad shard");
     t->tb.set_shard(rank, world);

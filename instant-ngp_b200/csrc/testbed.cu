@@ -185,6 +185,12 @@ void Testbed::train_begin(cudaStream_t s, uint32_t batch_size) {
     else train_image_step(s, batch_size, m_get_loss);
 }
 
+void Testbed::pending_counters(uint32_t* measured, uint32_t* measured_before) {
+    NGP_CHECK(m_pending_batch > 0 && m_mode == MODE_TB_NERF, "pending_counters: no Nerf training step in flight (call train_begin first)");
+    NGP_CUDA_CHECK(cudaEventSynchronize(m_ev_counters));
+    *measured = m_host_counters[2]; *measured_before = m_host_counters[1];
+}
+
 void Testbed::train_end(cudaStream_t s, uint32_t measured_override, uint32_t measured_before_override) {
     NGP_CHECK(m_pending_batch > 0, "train_end without train_begin");
     const uint32_t target = m_pending_batch; m_pending_batch = 0;

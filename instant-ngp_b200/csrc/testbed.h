@@ -41,6 +41,9 @@ public:
     void train_begin(cudaStream_t s, uint32_t batch_size);
     void train_end(cudaStream_t s, uint32_t measured_override, uint32_t measured_before_override);
     void set_shard(uint32_t rank, uint32_t world) { m_rank = rank; m_world = world; }
+    // local sample counts of the step begun by train_begin, available as soon as its loss kernel has run (the backward pass is
+    // still in flight): lets a data-parallel host exchange them while the device works
+    void pending_counters(uint32_t* measured, uint32_t* measured_before);
 
     // render_nerf (testbed_nerf.cu:2752-2871) into a host or device float4 buffer, rows [y0,y1), averaged over spp
     void render(cudaStream_t s, const float* camera_matrix, const float* focal_length, const float* screen_center, int w, int h, int spp, int y0, int y1,

@@ -151,9 +151,11 @@ class Testbed:
     # ---- training ----
     def enable_data_parallel(self, process_group=None):
         """Shard training rays over the ranks of a torch.distributed process group; gradients are summed with one
-        all_reduce over the flat fp16 gradient buffer per step (layout nerf_network.h:430-443)."""
+        all_reduce over the flat fp16 gradient buffer per step (layout nerf_network.h:430-443).  The two per-step sample
+        counters are exchanged on a side stream (NCCL) or on the host (gloo) while the backward pass is still running."""
         import torch.distributed as dist
-        object.__setattr__(self, "_dist", (dist, process_group))
+        side = torch.cuda.Stream() if dist.get_backend(process_group) == "nccl" else None
+        object.__setattr__(self, "_dist", (dist, process_group, side))
         check(lib().ngp_testbed_set_shard(self._h, dist.get_rank(process_group), dist.get_world_size(process_group)))
 
     def train(self, batch_size=None):
@@ -161,25 +163,31 @@ class Testbed:
         if self._dist is None:
             check(lib().ngp_testbed_train(self._h, _stream(), n))
             return
-        dist, pg = self._dist
+        dist, pg, side = self._dist
+        w = dist.get_world_size(pg)
         check(lib().ngp_testbed_train_begin(self._h, _stream(), n))
         g = self.param_buffer(3)
+        if self.mode == TestbedMode.Nerf:
+            # keep rays_per_batch in lock-step: the control law sees the mean sample counts.  The local counts are on the host
+            # as soon as the loss kernel has run; their all-reduce goes out on a side stream, i.e. NOT behind the backward pass
+            # that the training stream is still executing, and the host has the sums before the gradients are complete.
+            m, mb = C.c_uint32(), C.c_uint32()
+            check(lib().ngp_testbed_pending_counters(self._h, C.byref(m), C.byref(mb)))
+            if side is not None:
+                with torch.cuda.stream(side):
+                    c = torch.tensor([m.value, mb.value], dtype=torch.int64, device=g.device)
+                    dist.all_reduce(c, group=pg)
+                    c = c.cpu()
+            else:
+                c = torch.tensor([m.value, mb.value], dtype=torch.int64)
+                dist.all_reduce(c, group=pg)
+            m, mb = max(int(c[0]) // w, 1), max(int(c[1]) // w, 1)
+        else:
+            m, mb = 1, 1
+        # gradient sum: enqueued behind the backward pass; the optimizer (train_end) is ordered behind it on the stream, while
+        # the next step's ray prefetch, launched by train_end on its own stream, runs beside both
         dist.all_reduce(g, group=pg)
-        # keep rays_per_batch in lock-step: the control law sees the mean sample counts
-        st_before = self._local_counters()
-        c = torch.tensor(st_before, dtype=torch.int64, device=g.device)
-        dist.all_reduce(c, group=pg)
-        w = dist.get_world_size(pg)
-        m, mb = int(c[0].item()) // w, int(c[1].item()) // w
-        check(lib().ngp_testbed_train_end(self._h, _stream(), max(m, 1), max(mb, 1)))
-
-    def _local_counters(self):
-        ptr, nbytes = self.debug_buffer("counters")
-        if self.mode != TestbedMode.Nerf or not ptr:
-            return [1, 1]
-        t = _wrap(ptr, 4, torch.int32)
-        c = t.cpu().numpy().view(np.uint32)
-        return [int(c[2]), int(c[1])]
+        check(lib().ngp_testbed_train_end(self._h, _stream(), m, mb))
 
     def frame(self):
         if self.shall_train:
