@@ -137,6 +137,32 @@ def test_sampler_and_loss_bit_exact_compaction(env, ref, n_warm, lanes, prefetch
         np.testing.assert_allclose(gdl[nc:], gdl[src] * (nc / BATCH), rtol=2e-3, atol=1e-7)
 
 
+@pytest.mark.parametrize("lanes", [1, 8])
+def test_sampler_with_cascades_and_cone_angle(env, ref, lanes):
+    """aabb_scale 4: three occupancy cascades, cone angle 1/256 (exponential stepping through logf/expf) — the general,
+    non-flat marcher path.  libm and the GPU differ in the last ulp of logf/expf, so a step can fall on the other side of a
+    voxel boundary for an occasional ray: rays must agree exactly for almost all rays and the totals must be close."""
+    pyngp = env["pyngp"]
+    tb = pyngp.Testbed(pyngp.TestbedMode.Nerf)
+    tb.sampler_lanes_per_ray = lanes
+    tb.set_nerf_dataset(env["views"], aabb_scale=4)
+    tb.reload_network_from_json(SMALL_CFG)
+    rpb, max_inf, step = _step_and_capture(tb, ref, env, 3)
+    aabb = ref.make_aabb((-1.5, -1.5, -1.5), (2.5, 2.5, 2.5))
+    bf = tb.density_grid(1).cpu().numpy()
+    o = ref.generate_training_samples(rpb, aabb, max_inf, 1337, 1 + step * (1 << 32), env["images"], bf, 2, True, 1.0 / 256.0)
+    c = tb.debug_tensor("counters", torch.int32, 4).cpu().numpy().view(np.uint32)
+    ns_gpu = tb.debug_tensor("numsteps_all", torch.int32, rpb).cpu().numpy()
+    assert abs(int(c[1]) - int(o["numsteps_counter"])) <= 0.005 * int(o["numsteps_counter"]) + 8
+    assert abs(int(c[0]) - int(o["ray_counter"])) <= 0.005 * int(o["ray_counter"]) + 2
+    nr = int(min(c[0], o["ray_counter"]))
+    # per-ray sample counts of the walk, by original ray index (the compacted arrays are rewritten by the loss pass)
+    ref_idx = o["ray_indices"][:int(o["ray_counter"])]; ref_cnt = o["numsteps"][:int(o["ray_counter"]), 0]
+    same = int((ns_gpu[ref_idx] == ref_cnt.astype(ns_gpu.dtype)).sum())
+    assert same >= 0.98 * nr, (same, nr)
+    assert ns_gpu.max() > 0
+
+
 def test_marcher_variants_train_identically(env):
     """thread-per-ray, 8 and 32 lanes per ray: same samples and sample counts at every step of a 40-step run"""
     params = []
