@@ -215,7 +215,7 @@ def run_own(args):
     tb.set_nerf_dataset(views, aabb_scale=1)
     tb.reload_network_from_json(cfg)
     if world > 1:
-        tb.enable_data_parallel()
+        tb.enable_data_parallel(native=os.environ.get('NGP_DP_NATIVE', '1') == '1')
     batch = args.batch
 
     def barrier():

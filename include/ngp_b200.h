@@ -157,6 +157,14 @@ int ngp_testbed_train_end(ngp_testbed_t t, void* stream, uint32_t measured_batch
  * (NerfCounters, testbed.h:433-447) */
 int ngp_testbed_pending_counters(ngp_testbed_t t, uint32_t* measured_batch_size, uint32_t* measured_batch_size_before_compaction);
 int ngp_testbed_set_shard(ngp_testbed_t t, uint32_t rank, uint32_t world_size);
+/* Data-parallel step inside the library (ngp_comm_init / ngp_allreduce_gradients).  Rank 0 obtains an NCCL unique id
+ * (128 bytes), the host distributes it, every rank calls ngp_testbed_comm_init (collective).  From then on ngp_testbed_train
+ * shards the rays by rank, all-reduces the two sample counters under the backward pass and the fp16 gradient vector
+ * (layout nerf_network.h:430-443) slice by slice — MLP weights, then one hash-level chunk at a time — on a communication
+ * stream beside the remaining backward kernels; every rank then runs the identical optimizer step.  NCCL is bound at run
+ * time: nccl_lib_path names libnccl.so.2 (NULL: the copy already loaded in the process, $NGP_NCCL_LIB, or the system one). */
+int ngp_comm_unique_id(void* out_128_bytes, const char* nccl_lib_path);
+int ngp_testbed_comm_init(ngp_testbed_t t, const void* id_128_bytes, uint32_t rank, uint32_t world_size, const char* nccl_lib_path);
 int ngp_testbed_stats(ngp_testbed_t t, ngp_train_stats* out);
 uint64_t ngp_testbed_n_params(ngp_testbed_t t);                                         /* Testbed::n_params python_api.cu:440 */
 /* device pointers of the trainer's flat buffers (layout nerf_network.h:430-443): 0 master fp32, 1 params fp16,

@@ -224,6 +224,16 @@ int ngp_testbed_pending_counters(ngp_testbed_t t, uint32_t* measured, uint32_t* 
     t->tb.pending_counters(measured, measured_before);
     NGP_API_END
 }
+int ngp_comm_unique_id(void* out128, const char* nccl_lib_path) {
+    NGP_API_BEGIN NGP_CHECK(out128, "null argument");
+    Comm::unique_id(out128, nccl_lib_path);
+    NGP_API_END
+}
+int ngp_testbed_comm_init(ngp_testbed_t t, const void* id128, uint32_t rank, uint32_t world, const char* nccl_lib_path) {
+    NGP_API_BEGIN require_device(); NGP_CHECK(t && id128, "null argument");
+    t->tb.comm_init(id128, rank, world, nccl_lib_path);
+    NGP_API_END
+}
 int ngp_testbed_set_shard(ngp_testbed_t t, uint32_t rank, uint32_t world) {
     NGP_API_BEGIN NGP_CHECK(t && world >= 1 && rank < world, "bad shard");
     t->tb.set_shard(rank, world);

@@ -208,10 +208,10 @@ NGP_D void red_add_entry(__half* p, float w, const float* d) {
 
 template <uint32_t D, uint32_t F>
 __global__ void __launch_bounds__(256) grid_backward_kernel(const GridLayout g, const float* __restrict__ x, uint32_t x_stride, uint32_t n,
-                                                            const __half* __restrict__ dy, int dy_layout, __half* __restrict__ grad) {
+                                                            const __half* __restrict__ dy, int dy_layout, __half* __restrict__ grad, uint32_t chunk0) {
     constexpr uint32_t LPC = 8 / F;
     constexpr uint32_t NC = 1u << D;
-    const uint32_t row = blockIdx.x * blockDim.x + threadIdx.x, chunk = blockIdx.y;
+    const uint32_t row = blockIdx.x * blockDim.x + threadIdx.x, chunk = chunk0 + blockIdx.y;
     if (row >= n) return;
     size_t off = (dy_layout == LAYOUT_BLK8) ? blk8_chunk_offset(row, chunk, g.padded_width) : (size_t)row * g.padded_width + chunk * 8;
     const uint4 raw = __ldg(reinterpret_cast<const uint4*>(dy + off));
@@ -355,7 +355,17 @@ void grid_backward(cudaStream_t s, const GridLayout& g, const float* x, uint32_t
     if (n == 0) return;
     NGP_PROFILE_SCOPE(s, "grid_backward", n);
     const dim3 blocks(div_round_up(n, 256), g.padded_width / 8, 1);
-    GRID_DISPATCH(grid_backward_kernel, g, x, x_stride, n, dy, dy_layout, grad);
+    GRID_DISPATCH(grid_backward_kernel, g, x, x_stride, n, dy, dy_layout, grad, 0u);
+}
+
+// the same pass restricted to 8-feature chunks [chunk0, chunk0 + n_chunks): the data-parallel step launches it chunk by chunk
+// so that each chunk's slice of the gradient table can be all-reduced while the next chunk is still being scattered
+void grid_backward_chunks(cudaStream_t s, const GridLayout& g, const float* x, uint32_t x_stride, uint32_t n, const __half* dy,
+                          int dy_layout, __half* grad, uint32_t chunk0, uint32_t n_chunks) {
+    if (n == 0 || n_chunks == 0) return;
+    NGP_PROFILE_SCOPE(s, "grid_backward", n);
+    const dim3 blocks(div_round_up(n, 256), n_chunks, 1);
+    GRID_DISPATCH(grid_backward_kernel, g, x, x_stride, n, dy, dy_layout, grad, chunk0);
 }
 
 void grid_backward_input(cudaStream_t s, const GridLayout& g, const __half* table, const float* x, uint32_t x_stride,

@@ -5,6 +5,7 @@
 //   Optimizer             <-> tcnn::create_optimizer(json): Ema(ExponentialDecay(Adam)) (testbed.cu:4008, configs/nerf/base.json:5-22)
 //   Trainer               <-> tcnn::Trainer<float,T,T> (owns master/params/inference params/gradients)  (testbed.cu:4129)
 #pragma once
+#include <functional>
 #include "ngp_internal.h"
 #include "json_mini.h"
 #include <vector>
@@ -47,7 +48,8 @@ struct NerfNetwork {
     void forward_backward(cudaStream_t s, const __half* params, const float* coords, uint32_t n, const __half* dL_dout, __half* grads);
     // same, with the encoder outputs of the n samples already known (blk8 rows in enc_train_buf, carried over from inference())
     void forward_backward_encoded(cudaStream_t s, const __half* params, const float* coords, uint32_t n, const __half* dL_dout, __half* grads,
-                                  cudaEvent_t after_mlp = nullptr, bool grid_grads_clean = false);   // recorded between the MLP and the hash-grid backward kernels
+                                  cudaEvent_t after_mlp = nullptr, bool grid_grads_clean = false,
+                                  const std::function<void(size_t, size_t)>* slice_ready = nullptr);   // (offset, count) of `grads` complete on s   // recorded between the MLP and the hash-grid backward kernels
     const __half* last_inference_encoding() const { return enc_buf.as<__half>(); }
     __half* training_encoding(uint32_t n) { return enc_train_buf.get<__half>((size_t)n * dims.pos_width); }
 };

@@ -37,6 +37,8 @@ void grid_forward(cudaStream_t s, const GridLayout& g, const __half* table, cons
 // grad += scatter(w * dy); grad is table-shaped fp16 (caller zeroes it for EGradientMode::Overwrite)
 void grid_backward(cudaStream_t s, const GridLayout& g, const float* x, uint32_t x_stride, uint32_t n, const __half* dy,
                    int dy_layout, __half* grad);
+void grid_backward_chunks(cudaStream_t s, const GridLayout& g, const float* x, uint32_t x_stride, uint32_t n, const __half* dy,
+                          int dy_layout, __half* grad, uint32_t chunk0, uint32_t n_chunks);
 // dL/dx [n][n_dims] fp32
 void grid_backward_input(cudaStream_t s, const GridLayout& g, const __half* table, const float* x, uint32_t x_stride,
                          uint32_t n, const __half* dy, int dy_layout, float* dx);

@@ -23,6 +23,9 @@ Testbed::~Testbed() {
     if (m_ev_counters) cudaEventDestroy(m_ev_counters);
     if (m_ev_prefetch) cudaEventDestroy(m_ev_prefetch);
     if (m_ev_after_mlp) cudaEventDestroy(m_ev_after_mlp);
+    if (m_comm_stream) { cudaStreamSynchronize(m_comm_stream); cudaStreamDestroy(m_comm_stream); }
+    for (cudaEvent_t e : {m_ev_slice, m_ev_comm_done, m_ev_dp_counters}) if (e) cudaEventDestroy(e);
+    m_comm.reset();
     if (m_host_counters) cudaFreeHost(m_host_counters);
     for (void* p : m_image_buffers) cudaFree(p);
 }
@@ -185,6 +188,23 @@ void Testbed::train_begin(cudaStream_t s, uint32_t batch_size) {
     else train_image_step(s, batch_size, m_get_loss);
 }
 
+void Testbed::comm_init(const void* id128, uint32_t rank, uint32_t world, const char* nccl_lib_path) {
+    NGP_CHECK(m_mode == MODE_TB_NERF, "comm_init: data-parallel training is implemented for the Nerf mode");
+    NGP_CHECK(world >= 1 && rank < world, "comm_init: bad rank / world size");
+    m_comm = std::make_unique<Comm>(id128, (int)rank, (int)world, nccl_lib_path);
+    set_shard(rank, world);
+    if (!m_comm_stream) {
+        int least = 0, greatest = 0;
+        NGP_CUDA_CHECK(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+        NGP_CUDA_CHECK(cudaStreamCreateWithPriority(&m_comm_stream, cudaStreamNonBlocking, greatest));   // the collective's CTAs get their SMs first
+        NGP_CUDA_CHECK(cudaEventCreateWithFlags(&m_ev_slice, cudaEventDisableTiming));
+        NGP_CUDA_CHECK(cudaEventCreateWithFlags(&m_ev_comm_done, cudaEventDisableTiming));
+        NGP_CUDA_CHECK(cudaEventCreateWithFlags(&m_ev_dp_counters, cudaEventDisableTiming));
+    }
+    m_dp_counters.get<uint32_t>(2);
+    m_prefetch_valid = false;
+}
+
 void Testbed::pending_counters(uint32_t* measured, uint32_t* measured_before) {
     NGP_CHECK(m_pending_batch > 0 && m_mode == MODE_TB_NERF, "pending_counters: no Nerf training step in flight (call train_begin first)");
     NGP_CUDA_CHECK(cudaEventSynchronize(m_ev_counters));
@@ -210,6 +230,11 @@ void Testbed::train_end(cudaStream_t s, uint32_t measured_override, uint32_t mea
     }
     NGP_CUDA_CHECK(cudaEventSynchronize(m_ev_counters));
     const uint32_t* c = m_host_counters;
+    if (m_comm && !measured_override && !measured_before_override) {   // lock-step control law: the mean counts over the ranks
+        NGP_CUDA_CHECK(cudaEventSynchronize(m_ev_dp_counters));
+        measured_before_override = std::max(c[5] / (uint32_t)m_comm->world(), 1u);
+        measured_override = std::max(c[6] / (uint32_t)m_comm->world(), 1u);
+    }
     m_measured_before = measured_before_override ? measured_before_override : c[1];
     m_measured = measured_override ? measured_override : c[2];
     if (m_measured_before == 0 || m_measured == 0) {
@@ -314,6 +339,7 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
         NGP_CUDA_CHECK(cudaEventCreateWithFlags(&m_ev_prefetch, cudaEventDisableTiming));
         NGP_CUDA_CHECK(cudaEventCreateWithFlags(&m_ev_after_mlp, cudaEventDisableTiming));
         NGP_CUDA_CHECK(cudaMallocHost(&m_host_counters, 8 * sizeof(uint32_t)));
+        memset(m_host_counters, 0, 8 * sizeof(uint32_t));
     }
     const uint32_t max_samples = target * 16;
     const uint32_t R = m_rays_per_batch, max_rays = 1u << 18;
@@ -352,9 +378,32 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
     nerf_compute_loss(s, R, aabb, n_rays_total, m_rng, target, lc, m_n_images, m_metas.as<ImageMeta>(), m_mean.as<float>(), ray_offset, n_rays_global, sb, lb);
     NGP_CUDA_CHECK(cudaMemcpyAsync(m_host_counters, sb.counters, 16, cudaMemcpyDeviceToHost, s));   // read by train_end
     NGP_CUDA_CHECK(cudaEventRecord(m_ev_counters, s));
+    if (m_comm) {   // global sample counts for the control law: summed while the backward pass runs
+        uint32_t* dc = m_dp_counters.as<uint32_t>();
+        NGP_CUDA_CHECK(cudaMemcpyAsync(dc, sb.counters + 1, 8, cudaMemcpyDeviceToDevice, s));   // [1] before compaction, [2] compacted
+        NGP_CUDA_CHECK(cudaEventRecord(m_ev_slice, s));
+        NGP_CUDA_CHECK(cudaStreamWaitEvent(m_comm_stream, m_ev_slice, 0));
+        m_comm->all_reduce_sum(dc, 2, COMM_U32, m_comm_stream);
+        NGP_CUDA_CHECK(cudaMemcpyAsync(m_host_counters + 5, dc, 8, cudaMemcpyDeviceToHost, m_comm_stream));
+        NGP_CUDA_CHECK(cudaEventRecord(m_ev_dp_counters, m_comm_stream));
+    }
     nerf_fill_rollover(s, target, &sb.counters[2], lb.dloss_doutput, lb.coords_compacted, lb.enc_out, lb.enc_width);   // :4061-4069
     // forward(compacted) + backward(EGradientMode::Overwrite) (:4077-4078)
-    m_nerf_net->forward_backward_encoded(s, m_trainer->params, lb.coords_compacted, target, lb.dloss_doutput, m_trainer->grads, m_ev_after_mlp, m_trainer->grid_grads_clean);
+    if (m_comm) {
+        // every finished slice of the gradient vector (MLP weights, then one hash level chunk at a time) is summed over the ranks
+        // on the communication stream while the next chunk is still being scattered; Adam waits for the last one
+        __half* grads = m_trainer->grads;
+        const std::function<void(size_t, size_t)> slice_ready = [&](size_t off, size_t count) {
+            NGP_CUDA_CHECK(cudaEventRecord(m_ev_slice, s));
+            NGP_CUDA_CHECK(cudaStreamWaitEvent(m_comm_stream, m_ev_slice, 0));
+            m_comm->all_reduce_sum(grads + off, count, COMM_F16, m_comm_stream);
+        };
+        m_nerf_net->forward_backward_encoded(s, m_trainer->params, lb.coords_compacted, target, lb.dloss_doutput, grads, m_ev_after_mlp, m_trainer->grid_grads_clean, &slice_ready);
+        NGP_CUDA_CHECK(cudaEventRecord(m_ev_comm_done, m_comm_stream));
+        NGP_CUDA_CHECK(cudaStreamWaitEvent(s, m_ev_comm_done, 0));
+    } else {
+        m_nerf_net->forward_backward_encoded(s, m_trainer->params, lb.coords_compacted, target, lb.dloss_doutput, m_trainer->grads, m_ev_after_mlp, m_trainer->grid_grads_clean);
+    }
     m_trainer->grid_grads_clean = false;
     m_rng.advance();   // :4127
 }

@@ -5,6 +5,7 @@
 #include "network.h"
 #include "nerf_kernels.h"
 #include "image_kernels.h"
+#include "comm.h"
 #include <memory>
 #include <vector>
 
@@ -44,6 +45,10 @@ public:
     // local sample counts of the step begun by train_begin, available as soon as its loss kernel has run (the backward pass is
     // still in flight): lets a data-parallel host exchange them while the device works
     void pending_counters(uint32_t* measured, uint32_t* measured_before);
+    // attach an NCCL communicator (collective: every rank calls it with the same id): from then on train() is the data-parallel
+    // step — rays sharded by rank, sample counters and gradients all-reduced from inside the step, the gradient slices one hash
+    // level chunk at a time on a communication stream beside the remaining backward kernels
+    void comm_init(const void* id128, uint32_t rank, uint32_t world, const char* nccl_lib_path);
 
     // render_nerf (testbed_nerf.cu:2752-2871) into a host or device float4 buffer, rows [y0,y1), averaged over spp
     void render(cudaStream_t s, const float* camera_matrix, const float* focal_length, const float* screen_center, int w, int h, int spp, int y0, int y1,
@@ -116,7 +121,9 @@ private:
     DeviceBuffer m_coarse;   // dilated 16^3 coarse occupancy (ray classification), rebuilt with the bitfield
     DeviceBuffer m_mlp_out, m_dloss, m_coords_compacted, m_loss, m_ray_scratch, m_compacted_numsteps, m_loss_sum, m_t_before;
     cudaStream_t m_aux_stream = nullptr; cudaEvent_t m_ev_counters = nullptr, m_ev_prefetch = nullptr, m_ev_after_mlp = nullptr;
-    uint32_t* m_host_counters = nullptr;   // pinned: 4 counters + the loss sum
+    uint32_t* m_host_counters = nullptr;   // pinned: [0..3] counters, [4] loss sum, [5..6] all-reduced (before, measured)
+    std::unique_ptr<Comm> m_comm; cudaStream_t m_comm_stream = nullptr; cudaEvent_t m_ev_slice = nullptr, m_ev_comm_done = nullptr, m_ev_dp_counters = nullptr;
+    DeviceBuffer m_dp_counters;
     bool m_prefetch_valid = false, m_all_images_u8 = false; SamplerKey m_prefetch_key{}; uint32_t m_dataset_version = 0, m_last_set = 0;
     // image mode
     DeviceBuffer m_image; int m_image_w = 0, m_image_h = 0; DeviceBuffer m_img_pos, m_img_target, m_img_out, m_img_dl, m_img_loss;

@@ -10,6 +10,7 @@ All arithmetic runs in libngp_b200.so; torch only provides the CUDA stream and (
 NCCL process group that all-reduces the flat fp16 gradient buffer between train_begin() and train_end().
 """
 import ctypes as C
+import os
 import enum
 import json as _json
 
@@ -149,14 +150,39 @@ class Testbed:
         return lib().ngp_testbed_n_params(self._h)
 
     # ---- training ----
-    def enable_data_parallel(self, process_group=None):
-        """Shard training rays over the ranks of a torch.distributed process group; gradients are summed with one
-        all_reduce over the flat fp16 gradient buffer per step (layout nerf_network.h:430-443).  The two per-step sample
-        counters are exchanged on a side stream (NCCL) or on the host (gloo) while the backward pass is still running."""
+    def enable_data_parallel(self, process_group=None, native=None):
+        """Shard training rays over the ranks of a torch.distributed process group (collective: every rank calls it).
+        native (default with an NCCL group): the library gets its own NCCL communicator (the unique id travels over the
+        process group) and train() runs the whole data-parallel step inside it — counters and gradient slices all-reduced
+        on a communication stream beside the backward kernels.  Otherwise the gradients are summed from here with one
+        torch all_reduce over the flat fp16 gradient buffer between train_begin and train_end (layout nerf_network.h:430-443)."""
         import torch.distributed as dist
-        side = torch.cuda.Stream() if dist.get_backend(process_group) == "nccl" else None
+        rank, world = dist.get_rank(process_group), dist.get_world_size(process_group)
+        nccl = dist.get_backend(process_group) == "nccl"
+        if native is None:
+            native = nccl and self.mode == TestbedMode.Nerf
+        if native:
+            path = None
+            try:
+                import nvidia
+                for p in nvidia.__path__:
+                    cand = os.path.join(p, "nccl", "lib", "libnccl.so.2")
+                    if os.path.exists(cand):
+                        path = cand.encode()
+            except ImportError:
+                pass
+            buf = (C.c_uint8 * 128)()
+            if rank == 0:
+                check(lib().ngp_comm_unique_id(buf, path))
+            t = torch.tensor(list(buf), dtype=torch.uint8, device="cuda" if nccl else "cpu")
+            dist.broadcast(t, src=dist.get_global_rank(process_group, 0) if process_group is not None else 0, group=process_group)
+            ident = (C.c_uint8 * 128)(*t.cpu().tolist())
+            check(lib().ngp_testbed_comm_init(self._h, ident, rank, world, path))
+            object.__setattr__(self, "_dist", None)          # train() is the plain entry point: the step is data-parallel inside
+            return
+        side = torch.cuda.Stream() if nccl else None
         object.__setattr__(self, "_dist", (dist, process_group, side))
-        check(lib().ngp_testbed_set_shard(self._h, dist.get_rank(process_group), dist.get_world_size(process_group)))
+        check(lib().ngp_testbed_set_shard(self._h, rank, world))
 
     def train(self, batch_size=None):
         n = int(batch_size or self.training_batch_size)
