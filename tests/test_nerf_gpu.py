@@ -178,6 +178,28 @@ def test_marcher_variants_train_identically(env):
         assert np.linalg.norm(p - params[0][0]) <= 1e-2 * np.linalg.norm(params[0][0])
 
 
+def test_native_data_parallel_step_world_size_1(env):
+    """the in-library data-parallel step (NCCL communicator bound at run time, counters + gradient all-reduce on the
+    communication stream) with a single rank must train exactly like the plain step"""
+    import ctypes as C
+    _lib = importlib.import_module("instant-ngp_b200._lib")
+    lib = _lib.lib()
+    runs = []
+    for native in (False, True):
+        tb = _testbed(env)
+        if native:
+            ident = (C.c_uint8 * 128)()
+            _lib.check(lib.ngp_comm_unique_id(ident, None))
+            _lib.check(lib.ngp_testbed_comm_init(tb._h, ident, 0, 1, None))
+        trace = []
+        for _ in range(40):
+            tb.train(BATCH)
+            trace.append((tb.stats.rays_per_batch, tb.stats.measured_batch_size, tb.stats.measured_batch_size_before_compaction))
+        runs.append((trace, tb.param_buffer(0).cpu().numpy().copy()))
+    assert runs[0][0] == runs[1][0]
+    assert np.linalg.norm(runs[0][1] - runs[1][1]) <= 1e-2 * np.linalg.norm(runs[0][1])
+
+
 def test_rays_per_batch_control_law(env, ref):
     tb = _testbed(env)
     for _ in range(8):
