@@ -144,7 +144,9 @@ int ngp_testbed_reload_network_from_json(ngp_testbed_t t, const char* json);    
 /* load_training_data (python_api.cu:398) with in-memory views; uploads pixels host->device */
 int ngp_testbed_set_nerf_dataset(ngp_testbed_t t, void* stream, uint32_t n_images, const ngp_training_image* images, int32_t aabb_scale);
 /* nerf.training.set_image(frame_idx, img) (python_api.cu:49-67,583): replace one view's pixels (same size and type as
- * given to set_nerf_dataset) from HOST memory; the copy is ordered on `stream` */
+ * given to set_nerf_dataset) from HOST memory.  The copy is ordered after everything already queued on `stream` and before the
+ * next training step's loss kernel; RGBA8 views travel on an internal copy stream so that the upload runs beside the start of
+ * that step.  The host buffer must stay valid until the next ngp_testbed_train* call has returned. */
 int ngp_testbed_set_training_image(ngp_testbed_t t, void* stream, uint32_t frame_idx, const void* host_pixels);
 int ngp_testbed_set_image(ngp_testbed_t t, void* stream, const float* host_rgba, int32_t width, int32_t height);   /* image mode */
 int ngp_testbed_train(ngp_testbed_t t, void* stream, uint32_t batch_size);              /* Testbed::train, python_api.cu:426 */

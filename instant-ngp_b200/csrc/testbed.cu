@@ -24,6 +24,8 @@ Testbed::~Testbed() {
     if (m_ev_prefetch) cudaEventDestroy(m_ev_prefetch);
     if (m_ev_after_mlp) cudaEventDestroy(m_ev_after_mlp);
     if (m_comm_stream) { cudaStreamSynchronize(m_comm_stream); cudaStreamDestroy(m_comm_stream); }
+    if (m_copy_stream) { cudaStreamSynchronize(m_copy_stream); cudaStreamDestroy(m_copy_stream); }
+    for (cudaEvent_t e : {m_ev_copy_gate, m_ev_copy_done}) if (e) cudaEventDestroy(e);
     for (cudaEvent_t e : {m_ev_slice, m_ev_comm_done, m_ev_dp_counters}) if (e) cudaEventDestroy(e);
     m_comm.reset();
     if (m_host_counters) cudaFreeHost(m_host_counters);
@@ -70,6 +72,8 @@ void Testbed::set_nerf_dataset(cudaStream_t s, uint32_t n_images, const HostImag
     NGP_CHECK(aabb_scale >= 1 && (aabb_scale & (aabb_scale - 1)) == 0, "NeRF dataset's `aabb_scale` must be a power of two");
     NGP_CHECK(aabb_scale <= (1 << (NERF_CASCADES - 1)), "NeRF dataset must have `aabb_scale <= 128`");
     if (m_aux_stream) NGP_CUDA_CHECK(cudaStreamSynchronize(m_aux_stream));   // a ray prefetch in flight reads the old images
+    if (m_copy_stream) NGP_CUDA_CHECK(cudaStreamSynchronize(m_copy_stream));
+    m_copy_pending = false;
     m_prefetch_valid = false; ++m_dataset_version; m_all_images_u8 = true;
     for (void* p : m_image_buffers) cudaFree(p);
     m_image_buffers.clear(); m_image_bytes.clear();
@@ -118,7 +122,17 @@ void Testbed::set_training_image(cudaStream_t s, uint32_t frame_idx, const void*
     NGP_CHECK(frame_idx < m_n_images, "Invalid frame index");   // python_api.cu:50-52
     NGP_CHECK(pixels_host, "set_training_image: null pixels");
     if (!m_all_images_u8) { ++m_dataset_version; if (m_aux_stream) NGP_CUDA_CHECK(cudaStreamSynchronize(m_aux_stream)); }   // RGBA8 has no masked (negative) pixels: the walk never depends on its content
-    NGP_CUDA_CHECK(cudaMemcpyAsync(m_image_buffers[frame_idx], pixels_host, m_image_bytes[frame_idx], cudaMemcpyHostToDevice, s));
+    if (!m_all_images_u8) { NGP_CUDA_CHECK(cudaMemcpyAsync(m_image_buffers[frame_idx], pixels_host, m_image_bytes[frame_idx], cudaMemcpyHostToDevice, s)); return; }
+    if (!m_copy_stream) {
+        NGP_CUDA_CHECK(cudaStreamCreateWithFlags(&m_copy_stream, cudaStreamNonBlocking));
+        NGP_CUDA_CHECK(cudaEventCreateWithFlags(&m_ev_copy_gate, cudaEventDisableTiming));
+        NGP_CUDA_CHECK(cudaEventCreateWithFlags(&m_ev_copy_done, cudaEventDisableTiming));
+    }
+    NGP_CUDA_CHECK(cudaEventRecord(m_ev_copy_gate, s));                          // readers of the old pixels already queued on s
+    NGP_CUDA_CHECK(cudaStreamWaitEvent(m_copy_stream, m_ev_copy_gate, 0));
+    NGP_CUDA_CHECK(cudaMemcpyAsync(m_image_buffers[frame_idx], pixels_host, m_image_bytes[frame_idx], cudaMemcpyHostToDevice, m_copy_stream));
+    NGP_CUDA_CHECK(cudaEventRecord(m_ev_copy_done, m_copy_stream));
+    m_copy_pending = true;                                                       // the next loss kernel (the reader of pixel values) waits for it
 }
 
 void Testbed::set_image(cudaStream_t s, const float* rgba_host, int w, int h) {
@@ -375,6 +389,7 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
     memcpy(lc.background_color, background_color, sizeof(lc.background_color));
     lc.loss_scale = LOSS_SCALE; lc.near_distance = near_distance;
     lb.enc_in = m_nerf_net->last_inference_encoding();   // written by inference() just above
+    if (m_copy_pending) { NGP_CUDA_CHECK(cudaStreamWaitEvent(s, m_ev_copy_done, 0)); m_copy_pending = false; }   // uploaded view(s), see set_training_image
     nerf_compute_loss(s, R, aabb, n_rays_total, m_rng, target, lc, m_n_images, m_metas.as<ImageMeta>(), m_mean.as<float>(), ray_offset, n_rays_global, sb, lb);
     NGP_CUDA_CHECK(cudaMemcpyAsync(m_host_counters, sb.counters, 16, cudaMemcpyDeviceToHost, s));   // read by train_end
     NGP_CUDA_CHECK(cudaEventRecord(m_ev_counters, s));

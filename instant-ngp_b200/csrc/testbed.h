@@ -33,7 +33,9 @@ public:
     void set_nerf_dataset(cudaStream_t s, uint32_t n_images, const HostImage* images, int aabb_scale);
     void set_image(cudaStream_t s, const float* rgba_host, int w, int h);
     // nerf.training.set_image (python_api.cu:49-67): replace the pixels of one training view (same resolution / type),
-    // host -> device on `s`; asynchronous with respect to the host when the source is pinned
+    // host -> device; asynchronous with respect to the host when the source is pinned.  RGBA8 views are copied on an internal
+    // copy stream, ordered after everything already queued on `s` and before the next training step's loss kernel, so the
+    // upload runs beside the start of that step; the host buffer must stay valid until the next train call has returned
     void set_training_image(cudaStream_t s, uint32_t frame_idx, const void* pixels_host);
 
     // Testbed::train (testbed.cu:4285-4370): one step.  train_begin computes gradients, train_end runs the optimizer and
@@ -124,6 +126,7 @@ private:
     uint32_t* m_host_counters = nullptr;   // pinned: [0..3] counters, [4] loss sum, [5..6] all-reduced (before, measured)
     std::unique_ptr<Comm> m_comm; cudaStream_t m_comm_stream = nullptr; cudaEvent_t m_ev_slice = nullptr, m_ev_comm_done = nullptr, m_ev_dp_counters = nullptr;
     DeviceBuffer m_dp_counters;
+    cudaStream_t m_copy_stream = nullptr; cudaEvent_t m_ev_copy_gate = nullptr, m_ev_copy_done = nullptr; bool m_copy_pending = false;
     bool m_prefetch_valid = false, m_all_images_u8 = false; SamplerKey m_prefetch_key{}; uint32_t m_dataset_version = 0, m_last_set = 0;
     // image mode
     DeviceBuffer m_image; int m_image_w = 0, m_image_h = 0; DeviceBuffer m_img_pos, m_img_target, m_img_out, m_img_dl, m_img_loss;

@@ -200,6 +200,30 @@ def test_native_data_parallel_step_world_size_1(env):
     assert np.linalg.norm(runs[0][1] - runs[1][1]) <= 1e-2 * np.linalg.norm(runs[0][1])
 
 
+def test_set_training_image_replaces_the_targets(env):
+    """nerf.training.set_image (python_api.cu:49-67): pixels uploaded after the dataset was set are what the loss sees — a testbed
+    whose views were all replaced before the first step computes the same per-ray losses as one built from those pixels"""
+    views2 = []
+    for v in env["views"]:
+        px = v["pixels"].clone()
+        px[..., 0] = 255 - px[..., 0]                       # a different picture, same alpha
+        views2.append({**v, "pixels": px})
+    pyngp = env["pyngp"]
+    a = pyngp.Testbed(pyngp.TestbedMode.Nerf); a.set_nerf_dataset(views2, aabb_scale=1); a.reload_network_from_json(SMALL_CFG)
+    b = _testbed(env)
+    for i, v in enumerate(views2):
+        b.set_training_image(i, v["pixels"])
+    c = _testbed(env)                                        # the original pictures: must differ
+    out = []
+    for tb in (a, b, c):
+        tb.train(BATCH)
+        out.append(tb.debug_tensor("loss", torch.float32, tb.stats.rays_per_batch if False else 4096).cpu().numpy().copy())
+    np.testing.assert_allclose(out[1], out[0], rtol=1e-5, atol=1e-12)
+    assert np.abs(out[2] - out[0]).max() > 1e-9
+    with pytest.raises(Exception):
+        b.set_training_image(len(views2), views2[0]["pixels"])
+
+
 def test_rays_per_batch_control_law(env, ref):
     tb = _testbed(env)
     for _ in range(8):
