@@ -675,10 +675,10 @@ __global__ void __launch_bounds__(128) sampler_classify_kernel(uint32_t n_rays, 
 
 template <uint32_t G, bool FLAT, uint32_t K>
 __global__ void __launch_bounds__(SCAN_BLOCK) sampler_count_group_kernel(uint32_t n_rays, Aabb aabb, const uint8_t* __restrict__ bitfield, uint32_t max_mip, SamplerBuffers b) {
-    constexpr uint32_t RPB = SCAN_BLOCK / G;
+    constexpr uint32_t RPB = SCAN_BLOCK / G;           // rays per block of the ray-order scan (sampler_write_group_kernel), not of this launch
     const uint32_t lane = threadIdx.x % G, gshift = (threadIdx.x & 31u) / G * G;
     const uint32_t gmask = G == 32 ? 0xffffffffu : (((1u << G) - 1u) << gshift);
-    const uint32_t c = blockIdx.x * RPB + threadIdx.x / G;
+    const uint32_t c = blockIdx.x * (blockDim.x / G) + threadIdx.x / G;
     if (c >= b.counters[4]) return;   // group-uniform
     const uint32_t i = b.cand_list[c];
     const float* rt = b.ray_tmp + (size_t)i * 8;
@@ -788,7 +788,10 @@ void nerf_generate_training_samples(cudaStream_t s, uint32_t n_rays, Aabb aabb, 
     if (const char* e = getenv("NGP_SAMPLER_K")) K = (uint32_t)atoi(e);
     const bool flat = cone_angle_constant <= 1e-5f && max_mip == 0;
     const uint32_t blocks = div_round_up(n_rays, SCAN_BLOCK / G);
-#define NGP_SAMPLER_COUNT(GG, FF, KK) sampler_count_group_kernel<GG, FF, KK><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, bitfield, max_mip, b)
+    uint32_t count_block = 64;
+    if (const char* e = getenv("NGP_COUNT_BLOCK")) count_block = (uint32_t)atoi(e);
+// the walk has no block-wide step: small blocks (2 warps) spread the candidate rays evenly over the SMs
+#define NGP_SAMPLER_COUNT(GG, FF, KK) sampler_count_group_kernel<GG, FF, KK><<<div_round_up(n_rays, count_block / GG), count_block, 0, s>>>(n_rays, aabb, bitfield, max_mip, b)
 #define NGP_SAMPLER_COUNT_F(GG, KK) do { if (flat) NGP_SAMPLER_COUNT(GG, true, KK); else NGP_SAMPLER_COUNT(GG, false, KK); } while (0)
 #define NGP_SAMPLER_WRITE(GG) do { if (flat) sampler_write_group_kernel<GG, true><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, max_samples, bitfield, max_mip, b); \
                                    else sampler_write_group_kernel<GG, false><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, max_samples, bitfield, max_mip, b); } while (0)
