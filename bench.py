@@ -67,7 +67,7 @@ class ClockSampler:
 
     def __enter__(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "25"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
@@ -77,7 +77,7 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.lines.append(line.strip())
+            self.lines.append((time.time(), line.strip()))
 
     def __exit__(self, *a):
         if self.proc:
@@ -88,22 +88,28 @@ class ClockSampler:
             except subprocess.TimeoutExpired:
                 self.proc.kill()
 
-    def summary(self):
-        sm, mx, reasons = [], 0, set()
+    def summary(self, windows=None):
+        """median SM clock over the samples that arrived inside the given host-time windows (the timed regions); the sampler runs
+        from the untimed pre-training on, i.e. every sample is taken under the same training load"""
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for l in self.lines:
+        sm_in, sm_all, mx, reasons = [], [], 0, set()
+        for ts, l in self.lines:
             f = [x.strip() for x in l.split(",")]
             if len(f) < 7:
                 continue
             try:
-                sm.append(float(f[0])); mx = max(mx, float(f[1]))
+                v = float(f[0]); mx = max(mx, float(f[1]))
             except ValueError:
                 continue
-            for n, v in zip(names, f[3:7]):
-                if v.lower().startswith("active"):
+            sm_all.append(v)
+            if windows and any(a <= ts <= b + 0.03 for a, b in windows):
+                sm_in.append(v)
+            for n, x in zip(names, f[3:7]):
+                if x.lower().startswith("active"):
                     reasons.add(n)
-        sm.sort()
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons), "samples": len(sm)}
+        use = sorted(sm_in if sm_in else sm_all)
+        return {"sm_mhz": use[len(use) // 2] if use else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons), "samples": len(sm_in),
+                "samples_under_load": len(sm_all)}
 
 
 def measured_peaks():
@@ -224,6 +230,7 @@ def run_own(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    clk = ClockSampler(local).__enter__()      # runs from the untimed pre-training to the end of the e2e pass: every sample under the same training load
     for _ in range(args.pretrain + args.warmup):
         tb.train(batch)
 
@@ -253,11 +260,13 @@ def run_own(args):
     ncu = os.environ.get("NGP_NCU") == "1"      # under `ncu --profile-from-start off`: capture only the timed steps
     if ncu:
         torch.cuda.profiler.start()
-    with ClockSampler(local) as clk:
-        ms, n_samples, n_before, launches = timed(args.steps, upload=False)
+    t0 = time.time()
+    ms, n_samples, n_before, launches = timed(args.steps, upload=False)
+    t1 = time.time()
     if ncu:
         torch.cuda.profiler.stop()
-    clocks = clk.summary()
+    clk.__exit__()                              # (NVML polling during the upload pass was measured to slow the H2D copies: stop it first)
+    clocks = clk.summary([(t0, t1)])
     ms_e2e, n_e2e, _, _ = timed(args.steps, upload=True)
     view_bytes = int(views[0]["pixels"].numel())
     loss_steps = sum(1 for i in range(args.steps) if i % 16 == 0)
