@@ -149,6 +149,13 @@ int ngp_testbed_set_nerf_dataset(ngp_testbed_t t, void* stream, uint32_t n_image
  * that step.  The host buffer must stay valid until the next ngp_testbed_train* call has returned. */
 int ngp_testbed_set_training_image(ngp_testbed_t t, void* stream, uint32_t frame_idx, const void* host_pixels);
 int ngp_testbed_set_image(ngp_testbed_t t, void* stream, const float* host_rgba, int32_t width, int32_t height);   /* image mode */
+/* Sdf mode, Testbed::override_sdf_training_data (python_api.cu:69-99,437): n HOST (point xyz, signed distance) pairs in mesh
+ * space; raw_aabb_min/max and mesh_scale are what load_mesh derives from the mesh (m_raw_aabb, m_sdf.mesh_scale) and move the
+ * points into the unit cube (pass {0,0,0},{1,1,1},1 for data that is already there).  ngp_testbed_train then runs train_sdf
+ * (testbed_sdf.cu:1289-1311): the first batch_size records of a permutation keyed by the training step, config loss (MAPE for
+ * configs/sdf/base.json), optimizer.  As in the reference, a step is skipped when the data set is smaller than the batch. */
+int ngp_testbed_override_sdf_training_data(ngp_testbed_t t, void* stream, const float* host_points, const float* host_distances, uint32_t n,
+                                           const float* raw_aabb_min, const float* raw_aabb_max, float mesh_scale);
 int ngp_testbed_train(ngp_testbed_t t, void* stream, uint32_t batch_size);              /* Testbed::train, python_api.cu:426 */
 /* data-parallel split of train(): gradients only / optimizer + counters.  Between the two calls the caller all-reduces
  * (sum) the fp16 gradient buffer; measured_* = 0 keeps the local sample counts for the rays-per-batch control law. */

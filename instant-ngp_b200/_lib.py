@@ -90,6 +90,7 @@ SYMBOLS = {
     "ngp_testbed_set_nerf_dataset": (i32, [vp, vp, u32, vp, C.c_int32]),
     "ngp_testbed_set_training_image": (i32, [vp, vp, u32, vp]),
     "ngp_testbed_set_image": (i32, [vp, vp, vp, C.c_int32, C.c_int32]),
+    "ngp_testbed_override_sdf_training_data": (i32, [vp, vp, vp, vp, u32, vp, vp, f32]),
     "ngp_testbed_train": (i32, [vp, vp, u32]),
     "ngp_testbed_train_begin": (i32, [vp, vp, u32]),
     "ngp_testbed_train_end": (i32, [vp, vp, u32, u32]),

@@ -204,6 +204,12 @@ int ngp_testbed_set_image(ngp_testbed_t t, void* stream, const float* rgba, int3
     t->tb.set_image(S(stream), rgba, w, h);
     NGP_API_END
 }
+int ngp_testbed_override_sdf_training_data(ngp_testbed_t t, void* stream, const float* points, const float* distances, uint32_t n,
+                                           const float* raw_aabb_min, const float* raw_aabb_max, float mesh_scale) {
+    NGP_API_BEGIN require_device(); NGP_CHECK(t && raw_aabb_min && raw_aabb_max, "null argument");
+    t->tb.override_sdf_training_data(S(stream), points, distances, n, raw_aabb_min, raw_aabb_max, mesh_scale);
+    NGP_API_END
+}
 int ngp_testbed_train(ngp_testbed_t t, void* stream, uint32_t batch) {
     NGP_API_BEGIN require_device(); NGP_CHECK(t, "null argument");
     t->tb.train(S(stream), batch);

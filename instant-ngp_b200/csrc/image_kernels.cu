@@ -56,28 +56,6 @@ __global__ void image_eval_coords_kernel(uint32_t n, uint32_t offset, const floa
     target[(size_t)i * 3] = v[0]; target[(size_t)i * 3 + 1] = v[1]; target[(size_t)i * 3 + 2] = v[2];
 }
 
-// tcnn L2 loss: value = diff^2 / (n*3), gradient = loss_scale * 2 * diff / (n*3); prediction fp16 [n][16]
-__global__ void l2_loss_kernel(uint32_t n, const __half* __restrict__ pred, const float* __restrict__ target, float loss_scale, __half* __restrict__ dL,
-                               float* __restrict__ loss_values) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const float n_total = (float)n * 3.0f;
-    __half2 o[8];
-    float l = 0.f, g[3];
-#pragma unroll
-    for (int c = 0; c < 3; ++c) {
-        const float diff = __half2float(pred[(size_t)i * 16 + c]) - target[(size_t)i * 3 + c];
-        l += diff * diff / n_total;
-        g[c] = loss_scale * 2.0f * diff / n_total;
-    }
-#pragma unroll
-    for (int k = 0; k < 8; ++k) o[k] = __floats2half2_rn(0.f, 0.f);
-    o[0] = __floats2half2_rn(g[0], g[1]); o[1] = __floats2half2_rn(g[2], 0.f);
-    reinterpret_cast<uint4*>(dL + (size_t)i * 16)[0] = reinterpret_cast<uint4*>(o)[0];
-    reinterpret_cast<uint4*>(dL + (size_t)i * 16)[1] = reinterpret_cast<uint4*>(o)[1];
-    if (loss_values) loss_values[i] = l;
-}
-
 // image_mse_kernel (testbed_image.cu:452-463)
 __global__ void image_se_kernel(uint32_t n, const float* __restrict__ target, const __half* __restrict__ pred, float* __restrict__ se, bool quantize) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -101,10 +79,6 @@ void image_generate_batch(cudaStream_t s, uint32_t n, Pcg32 rng, bool stratify, 
 }
 void image_eval_coords(cudaStream_t s, uint32_t n, uint32_t offset, const float* image, int W, int H, bool linear_colors, float* pos, float* target) {
     image_eval_coords_kernel<<<div_round_up(n, 256), 256, 0, s>>>(n, offset, image, W, H, linear_colors, pos, target);
-    NGP_POST_LAUNCH();
-}
-void l2_loss(cudaStream_t s, uint32_t n, const __half* pred, const float* target, float loss_scale, __half* dL, float* loss_values) {
-    l2_loss_kernel<<<div_round_up(n, 256), 256, 0, s>>>(n, pred, target, loss_scale, dL, loss_values);
     NGP_POST_LAUNCH();
 }
 void image_squared_error(cudaStream_t s, uint32_t n, const float* target, const __half* pred, float* se, bool quantize) {

@@ -7,6 +7,13 @@
 
 namespace ngp {
 
+static int tcnn_loss_from_string(const std::string& s) {   // tcnn::create_loss otypes used by the image / SDF configs
+    const std::string l = to_lower(s);
+    if (l == "l2") return TLOSS_L2; if (l == "relativel2") return TLOSS_RELATIVE_L2; if (l == "l1") return TLOSS_L1;
+    if (l == "mape") return TLOSS_MAPE; if (l == "smape") return TLOSS_SMAPE;
+    throw Error("Unknown loss type '" + s + "'");
+}
+
 static int loss_type_from_string(const std::string& s) {   // string_to_loss_type (testbed.cu:3872-3891)
     const std::string l = to_lower(s);
     if (l == "l2") return LOSS_L2; if (l == "l1") return LOSS_L1; if (l == "mape") return LOSS_MAPE; if (l == "smape") return LOSS_SMAPE;
@@ -15,7 +22,7 @@ static int loss_type_from_string(const std::string& s) {   // string_to_loss_typ
 }
 
 Testbed::Testbed(int mode) : m_mode(mode), m_rng(1337), m_density_grid_rng(1337) {
-    NGP_CHECK(mode == MODE_TB_NERF || mode == MODE_TB_IMAGE, "Testbed: only the Nerf and Image modes are implemented on this path");
+    NGP_CHECK(mode == MODE_TB_NERF || mode == MODE_TB_IMAGE || mode == MODE_TB_SDF, "Testbed: unknown mode (Nerf = 0, Sdf = 1, Image = 2)");
 }
 
 Testbed::~Testbed() {
@@ -57,7 +64,9 @@ void Testbed::reset_network() {
             NGP_CUDA_CHECK(cudaMemset(m_bitfield.ptr, 0, m_bitfield.bytes));
         }
     } else {
-        m_image_net = std::make_unique<EncodedMlp>(m_config, 2, 3);
+        // Trainer(network, optimizer, create_loss(config["loss"])) (testbed.cu:4007,4129); image: 2-D -> rgb, SDF: 3-D -> distance
+        m_tcnn_loss = tcnn_loss_from_string(m_config.contains("loss") ? m_config.at("loss").value("otype", "L2") : std::string("L2"));
+        m_image_net = m_mode == MODE_TB_SDF ? std::make_unique<EncodedMlp>(m_config, 3, 1) : std::make_unique<EncodedMlp>(m_config, 2, 3);
         m_trainer = std::make_unique<Trainer>(m_image_net->n_params, m_image_net->n_matrix_params, opt);
         m_image_net->initialize_params(seed, m_trainer->master, 0);
     }
@@ -199,6 +208,7 @@ void Testbed::train_begin(cudaStream_t s, uint32_t batch_size) {
     m_get_loss = m_training_step % 16 == 0;
     m_pending_batch = batch_size;
     if (m_mode == MODE_TB_NERF) train_nerf_step(s, batch_size);
+    else if (m_mode == MODE_TB_SDF) train_sdf_step(s, batch_size, m_get_loss);
     else train_image_step(s, batch_size, m_get_loss);
 }
 
@@ -228,9 +238,10 @@ void Testbed::pending_counters(uint32_t* measured, uint32_t* measured_before) {
 void Testbed::train_end(cudaStream_t s, uint32_t measured_override, uint32_t measured_before_override) {
     NGP_CHECK(m_pending_batch > 0, "train_end without train_begin");
     const uint32_t target = m_pending_batch; m_pending_batch = 0;
+    if (m_mode == MODE_TB_SDF && m_sdf_step_skipped) return;   // train_sdf does nothing when the data set is smaller than the batch (testbed_sdf.cu:1293)
     m_trainer->optimizer_step(s, LOSS_SCALE);   // testbed_nerf.cu:3678 / testbed_image.cu:283
     ++m_training_step;
-    if (m_mode == MODE_TB_IMAGE) {
+    if (m_mode == MODE_TB_IMAGE || m_mode == MODE_TB_SDF) {
         if (m_get_loss) { NGP_CUDA_CHECK(cudaMemcpyAsync(&m_loss_scalar, m_loss_sum.as<float>(), 4, cudaMemcpyDeviceToHost, s)); }
         NGP_CUDA_CHECK(cudaStreamSynchronize(s));
         return;
@@ -434,9 +445,47 @@ void Testbed::train_image_step(cudaStream_t s, uint32_t n, bool get_loss) {
     image_generate_batch(s, n, m_rng, image_stratified, m_image.as<float>(), m_image_w, m_image_h, image_snap_to_pixel_centers, image_linear_colors, pos, target);
     m_rng.advance();
     m_image_net->inference(s, m_trainer->params, pos, 2, n, out);
-    l2_loss(s, n, out, target, LOSS_SCALE, dl, get_loss ? lossv : nullptr);
+    tcnn_loss(s, m_tcnn_loss, n, 3, out, target, LOSS_SCALE, dl, get_loss ? lossv : nullptr);
     if (get_loss) reduce_sum_f32(s, lossv, n, m_loss_sum.as<float>(), m_partials.as<float>());
     m_image_net->forward_backward(s, m_trainer->params, pos, 2, n, dl, m_trainer->grads);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// SDF mode with caller-supplied ground truth: override_sdf_training_data (python_api.cu:69-99) + train_sdf
+// (testbed_sdf.cu:1289-1311).  Generating ground truth from a mesh (BVH / OptiX) is outside the path.
+// ---------------------------------------------------------------------------------------------------------------
+void Testbed::override_sdf_training_data(cudaStream_t s, const float* points, const float* distances, uint32_t n, const float* raw_aabb_min,
+                                         const float* raw_aabb_max, float mesh_scale) {
+    NGP_CHECK(m_mode == MODE_TB_SDF, "override_sdf_training_data: testbed is not in Sdf mode");
+    NGP_CHECK(points && distances && n > 0, "Invalid Points<->Distances data");   // python_api.cu:73-76
+    NGP_CHECK(mesh_scale > 0.f, "override_sdf_training_data: mesh_scale must be positive");
+    // mesh space -> unit cube, as load_mesh leaves m_raw_aabb / mesh_scale (python_api.cu:85-86)
+    std::vector<float> p((size_t)n * 3), d(n);
+    for (uint32_t i = 0; i < n; ++i) {
+        for (int k = 0; k < 3; ++k)
+            p[(size_t)i * 3 + k] = (points[(size_t)i * 3 + k] - raw_aabb_min[k]) / mesh_scale + 0.5f * (1.0f - (raw_aabb_max[k] - raw_aabb_min[k]) / mesh_scale);
+        d[i] = distances[i] / mesh_scale;
+    }
+    NGP_CUDA_CHECK(cudaMemcpyAsync(m_sdf_pos.get<float>((size_t)n * 3), p.data(), (size_t)n * 12, cudaMemcpyHostToDevice, s));
+    NGP_CUDA_CHECK(cudaMemcpyAsync(m_sdf_dist.get<float>(n), d.data(), (size_t)n * 4, cudaMemcpyHostToDevice, s));
+    NGP_CUDA_CHECK(cudaStreamSynchronize(s));
+    m_sdf_size = n;
+}
+
+void Testbed::train_sdf_step(cudaStream_t s, uint32_t target_batch_size, bool get_loss) {
+    NGP_CHECK(m_sdf_size > 0, "Cannot train without training data");
+    m_sdf_step_skipped = m_sdf_size < target_batch_size;
+    if (m_sdf_step_skipped) return;
+    const uint32_t n = target_batch_size;   // min(size, target) with size >= target
+    float* pos = m_img_pos.get<float>((size_t)n * 3); float* target = m_img_target.get<float>(n);
+    __half* out = m_img_out.get<__half>((size_t)n * 16); __half* dl = m_img_dl.get<__half>((size_t)n * 16);
+    float* lossv = m_img_loss.get<float>(n); m_loss_sum.get<float>(4); m_partials.get<float>(1024);
+    // "Permute all training records to de-correlate training data": the first n records of permutation(seed = training step)
+    sdf_shuffle(s, m_sdf_size, n, m_training_step, m_sdf_pos.as<float>(), m_sdf_dist.as<float>(), pos, target);
+    m_image_net->inference(s, m_trainer->params, pos, 3, n, out);
+    tcnn_loss(s, m_tcnn_loss, n, 1, out, target, LOSS_SCALE, dl, get_loss ? lossv : nullptr);
+    if (get_loss) reduce_sum_f32(s, lossv, n, m_loss_sum.as<float>(), m_partials.as<float>());
+    m_image_net->forward_backward(s, m_trainer->params, pos, 3, n, dl, m_trainer->grads);
 }
 
 // compute_image_mse (testbed_image.cu:465-527): all pixels at pixel centres, inference params, chunks of 2^20
@@ -521,7 +570,7 @@ void Testbed::debug_buffer(const std::string& name, void** ptr, uint64_t* bytes)
                        {"mlp_out", &m_mlp_out}, {"dloss", &m_dloss}, {"coords_compacted", &m_coords_compacted}, {"loss", &m_loss},
                        {"grid_pos", &m_grid_pos}, {"grid_idx", &m_grid_idx}, {"grid_out", &m_grid_out}, {"density_grid_tmp", &m_density_grid_tmp},
                        {"mean_density", &m_mean}, {"numsteps_all", &m_numsteps_all[k]}, {"image_pos", &m_img_pos}, {"image_target", &m_img_target},
-                       {"image_out", &m_img_out}, {"image_dl", &m_img_dl}};
+                       {"image_out", &m_img_out}, {"image_dl", &m_img_dl}, {"sdf_positions", &m_sdf_pos}, {"sdf_distances", &m_sdf_dist}};
     for (const E& e : table) if (name == e.n) { *ptr = e.b->ptr; *bytes = e.b->bytes; return; }
     throw Error("debug_buffer: unknown buffer '" + name + "'");
 }

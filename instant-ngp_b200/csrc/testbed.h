@@ -5,6 +5,7 @@
 #include "network.h"
 #include "nerf_kernels.h"
 #include "image_kernels.h"
+#include "sdf_kernels.h"
 #include "comm.h"
 #include <memory>
 #include <vector>
@@ -32,6 +33,10 @@ public:
     // load_training_data equivalents with host buffers (NerfDataset: nerf_loader.h:110-171; load_nerf_post testbed_nerf.cu:3046-3112)
     void set_nerf_dataset(cudaStream_t s, uint32_t n_images, const HostImage* images, int aabb_scale);
     void set_image(cudaStream_t s, const float* rgba_host, int w, int h);
+    // override_sdf_training_data (python_api.cu:69-99): n host (point, signed distance) pairs in mesh space, moved into the unit
+    // cube with the mesh's raw bounding box and scale; from then on train() runs train_sdf on them (testbed_sdf.cu:1289-1311)
+    void override_sdf_training_data(cudaStream_t s, const float* points, const float* distances, uint32_t n, const float* raw_aabb_min,
+                                    const float* raw_aabb_max, float mesh_scale);
     // nerf.training.set_image (python_api.cu:49-67): replace the pixels of one training view (same resolution / type),
     // host -> device; asynchronous with respect to the host when the source is pinned.  RGBA8 views are copied on an internal
     // copy stream, ordered after everything already queued on `s` and before the next training step's loss kernel, so the
@@ -87,6 +92,7 @@ private:
     void update_density_grid_nerf(cudaStream_t s, float decay, uint32_t n_uniform, uint32_t n_nonuniform);   // :3412-3536
     void train_nerf_step(cudaStream_t s, uint32_t target_batch_size);                              // :3867-4132
     void train_image_step(cudaStream_t s, uint32_t batch_size, bool get_loss);                     // testbed_image.cu:214-285
+    void train_sdf_step(cudaStream_t s, uint32_t batch_size, bool get_loss);                       // testbed_sdf.cu:1289-1311
     struct SamplerKey {   // everything generate_training_samples depends on besides the bitfield and the view poses
         uint32_t step, n_rays, max_inference, target, rank, world, lanes, dataset_version; uint64_t rng_state, rng_inc; float cone; bool snap;
         bool operator==(const SamplerKey& o) const {
@@ -130,6 +136,8 @@ private:
     bool m_prefetch_valid = false, m_all_images_u8 = false; SamplerKey m_prefetch_key{}; uint32_t m_dataset_version = 0, m_last_set = 0;
     // image mode
     DeviceBuffer m_image; int m_image_w = 0, m_image_h = 0; DeviceBuffer m_img_pos, m_img_target, m_img_out, m_img_dl, m_img_loss;
+    // SDF mode (scratch shared with the image mode)
+    DeviceBuffer m_sdf_pos, m_sdf_dist; uint32_t m_sdf_size = 0; bool m_sdf_step_skipped = false; int m_tcnn_loss = TLOSS_L2;
     // render scratch
     DeviceBuffer m_r_rgba[3], m_r_depth[3], m_r_payload[3], m_r_input, m_r_output, m_r_counters, m_r_scan, m_frame, m_frame_depth, m_accum;
 };

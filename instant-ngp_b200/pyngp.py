@@ -137,6 +137,16 @@ class Testbed:
         assert rgba.ndim == 3 and rgba.shape[2] == 4
         check(lib().ngp_testbed_set_image(self._h, _stream(), rgba.ctypes.data_as(C.c_void_p), rgba.shape[1], rgba.shape[0]))
 
+    def override_sdf_training_data(self, points, distances, raw_aabb=((0.0, 0.0, 0.0), (1.0, 1.0, 1.0)), mesh_scale=1.0):
+        """Testbed.override_sdf_training_data(points [n,3], distances [n]) (python_api.cu:69-99).  raw_aabb / mesh_scale are what
+        the reference takes from the loaded mesh; the defaults mean "already in the unit cube"."""
+        points = np.ascontiguousarray(points, np.float32); distances = np.ascontiguousarray(distances, np.float32)
+        if points.ndim != 2 or distances.ndim != 1 or points.shape[0] != distances.shape[0] or points.shape[1] != 3:
+            raise RuntimeError("Invalid Points<->Distances data")
+        lo, hi = (C.c_float * 3)(*raw_aabb[0]), (C.c_float * 3)(*raw_aabb[1])
+        check(lib().ngp_testbed_override_sdf_training_data(self._h, _stream(), points.ctypes.data_as(C.c_void_p), distances.ctypes.data_as(C.c_void_p),
+                                                           points.shape[0], lo, hi, float(mesh_scale)))
+
     # ---- network ----
     def reload_network_from_json(self, config, config_base_path=""):
         cfg = config if isinstance(config, str) else _json.dumps(config)

@@ -78,6 +78,11 @@ def lib():
         l.ref_update_bitfield.restype = f32
         l.ref_l2_loss.restype = C.c_double
         l.ref_l2_loss.argtypes = [vp, u32, vp, u32, f32, vp]
+        l.ref_tcnn_loss.restype = C.c_double
+        l.ref_tcnn_loss.argtypes = [i32, vp, u32, vp, u32, u32, f32, vp]
+        l.ref_permute.restype = u32; l.ref_permute.argtypes = [u32, u32, u32]
+        l.ref_sdf_shuffle.argtypes = [u32, u32, u32, vp, vp, vp, vp]
+        l.ref_sdf_normalize.argtypes = [u32, vp, vp, vp, vp, f32, vp, vp]
         l.ref_next_rays_per_batch.restype = u32
         for name in ["ref_to_stepping_space", "ref_from_stepping_space", "ref_calc_dt", "ref_srgb_to_linear", "ref_linear_to_srgb"]:
             getattr(l, name).restype = f32
@@ -292,3 +297,31 @@ def synth_views(n_views, w, h, radius, focal, step=1.73205080757 / 1024.0, count
         l.ref_synth_camera(u32(i), u32(n_views), f32(radius), P(xf))
         views.append({"pixels": px.view(np.uint8).reshape(h, w, 4), "focal_length": (focal, focal), "principal_point": (0.5, 0.5), "xform": xf})
     return views
+
+
+TCNN_LOSS = {"L2": 0, "RelativeL2": 1, "L1": 2, "MAPE": 3, "SMAPE": 4}
+
+
+def sdf_shuffle(positions, distances, n_out, seed):
+    """first n_out records of tcnn shuffle(seed) over (positions [n,3], distances [n])"""
+    positions = np.ascontiguousarray(positions, np.float32); distances = np.ascontiguousarray(distances, np.float32)
+    po, do = np.empty((n_out, 3), np.float32), np.empty(n_out, np.float32)
+    lib().ref_sdf_shuffle(u32(len(distances)), u32(n_out), u32(seed), P(positions), P(distances), P(po), P(do))
+    return po, do
+
+
+def sdf_normalize(points, distances, raw_min, raw_max, mesh_scale):
+    points = np.ascontiguousarray(points, np.float32); distances = np.ascontiguousarray(distances, np.float32)
+    lo, hi = np.asarray(raw_min, np.float32), np.asarray(raw_max, np.float32)
+    po, do = np.empty_like(points), np.empty_like(distances)
+    lib().ref_sdf_normalize(u32(len(distances)), P(points), P(distances), P(lo), P(hi), f32(mesh_scale), P(po), P(do))
+    return po, do
+
+
+def tcnn_loss(kind, pred_h, target, dims, loss_scale=128.0):
+    """pred_h fp16 [n, stride]; target fp32 [n, dims] -> (summed loss, dL fp16 [n, stride])"""
+    pred_h = np.ascontiguousarray(pred_h, np.float16); target = np.ascontiguousarray(target, np.float32)
+    n, stride = pred_h.shape
+    dl = np.empty((n, stride), np.float16)
+    total = lib().ref_tcnn_loss(i32(TCNN_LOSS[kind]), P(pred_h), u32(stride), P(target), u32(n), u32(dims), f32(loss_scale), P(dl))
+    return total, dl

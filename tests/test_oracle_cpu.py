@@ -203,3 +203,41 @@ def test_product_fails_loudly_without_gpu(ops):
     _lib = importlib.import_module("instant-ngp_b200._lib")
     st = _lib.lib().ngp_encoding_initialize_params(e._h, None, 1, C.c_void_p(16))
     assert st != 0 and b"no CUDA device" in _lib.lib().ngp_last_error()
+
+
+def test_sdf_permutation_is_a_bijection(ref):
+    # tcnn shuffle(seed = training step): every record appears exactly once, for power-of-two and ragged sizes
+    for l in (1, 2, 3, 255, 256, 1000, 50_000):
+        for seed in (0, 1, 12345):
+            idx = np.array([ref.lib().ref_permute(i, l, seed) for i in range(min(l, 4096))])
+            assert idx.max() < l and len(np.unique(idx)) == len(idx)
+    pos = np.arange(30, dtype=np.float32).reshape(10, 3); dist = np.arange(10, dtype=np.float32)
+    p, d = ref.sdf_shuffle(pos, dist, 10, 7)
+    assert sorted(d.tolist()) == list(range(10)) and np.array_equal(p[:, 0], d * 3)      # positions and distances stay paired
+    assert not np.array_equal(d, ref.sdf_shuffle(pos, dist, 10, 8)[1])                    # another step, another order
+
+
+def test_tcnn_losses_gradient_is_the_derivative_of_the_value(ref):
+    rng = np.random.default_rng(0)
+    n, dims = 64, 3
+    pred = rng.normal(0, 1, (n, 16)).astype(np.float16); target = rng.normal(0, 1, (n, dims)).astype(np.float32)
+    for kind in ref.TCNN_LOSS:
+        total, dl = ref.tcnn_loss(kind, pred, target, dims, loss_scale=1.0)
+        assert total > 0 and not dl[:, dims:].any()
+        # finite difference in fp64 of the same formula (value is per element, so d total / d pred[i,c] = dl[i,c])
+        # (the relative losses hold their normaliser, evaluated at the prediction p0, constant)
+        def value(p, t, p0):
+            d = p - t
+            return {"L2": d * d, "RelativeL2": d * d / (p0 * p0 + 0.01), "L1": abs(d), "MAPE": abs(d) / (abs(t) + 0.01),
+                    "SMAPE": abs(d) / (0.5 * (abs(p0) + abs(t)) + 0.01)}[kind] / (n * dims)
+        p64 = pred[:, :dims].astype(np.float64); t64 = target.astype(np.float64)
+        eps = 1e-6
+        fd = (value(p64 + eps, t64, p64) - value(p64 - eps, t64, p64)) / (2 * eps)
+        ok = np.abs(p64 - t64) > 1e-3                                                    # away from the kink of |.|
+        np.testing.assert_allclose(dl[:, :dims].astype(np.float64)[ok], fd[ok], rtol=5e-3, atol=1e-6)
+        np.testing.assert_allclose(total, value(p64, t64, p64).sum(), rtol=1e-5)
+    # L2 agrees with the image step's loss
+    rdl = np.zeros((n, 16), np.float16)
+    t2 = ref.lib().ref_l2_loss(ref.P(pred), 16, ref.P(target), n, 128.0, ref.P(rdl))
+    total, dl = ref.tcnn_loss("L2", pred, target, 3, 128.0)
+    assert np.array_equal(dl, rdl) and abs(total - t2) < 1e-9
