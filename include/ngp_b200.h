@@ -176,6 +176,20 @@ int ngp_comm_unique_id(void* out_128_bytes, const char* nccl_lib_path);
 int ngp_testbed_comm_init(ngp_testbed_t t, const void* id_128_bytes, uint32_t rank, uint32_t world_size, const char* nccl_lib_path);
 int ngp_testbed_stats(ngp_testbed_t t, ngp_train_stats* out);
 uint64_t ngp_testbed_n_params(ngp_testbed_t t);                                         /* Testbed::n_params python_api.cu:440 */
+uint64_t ngp_testbed_n_encoding_params(ngp_testbed_t t);                                /* Testbed::n_encoding_params python_api.cu:445 */
+/* Testbed::save_snapshot(path, include_optimizer_state, compress) / load_snapshot(path) (python_api.cu:446-447; testbed.cu:4873-5057):
+ * MessagePack of the network config + "snapshot" {n_params, params_type "__half", params_binary (fp16 inference parameters),
+ * density_grid_size 128, density_grid_binary (fp16), nerf{aabb_scale, rgb{rays_per_batch, measured_batch_size, ...}, dataset{...}},
+ * training_step, loss, aabb, render_aabb, background_color, version 1, mode, [optimizer]}; a path ending in ".ingp" is wrapped in a
+ * zlib stream (compress = 0: stored), anything else (".msgpack") is written bare.  load_snapshot rebuilds the network from the
+ * embedded config, so the testbed needs no prior reload_network call; its mode must be the snapshot's. */
+/* host-only helpers of the snapshot codec (no device needed): a network config as JSON text (comments allowed, as the reference
+ * parses it) -> MessagePack, and decode + re-encode of a MessagePack buffer (what load_snapshot followed by save_snapshot does to the
+ * embedded config).  *out_size receives the encoded size; status 1 when `capacity` is too small or the input is malformed. */
+int ngp_json_to_msgpack(const char* json, void* out, uint64_t capacity, uint64_t* out_size);
+int ngp_msgpack_roundtrip(const void* in, uint64_t in_size, void* out, uint64_t capacity, uint64_t* out_size);
+int ngp_testbed_save_snapshot(ngp_testbed_t t, void* stream, const char* path, int32_t include_optimizer_state, int32_t compress);
+int ngp_testbed_load_snapshot(ngp_testbed_t t, void* stream, const char* path);
 /* device pointers of the trainer's flat buffers (layout nerf_network.h:430-443): 0 master fp32, 1 params fp16,
  * 2 inference params fp16 (EMA), 3 gradients fp16 */
 int ngp_testbed_param_buffer(ngp_testbed_t t, int which, void** dev_ptr, uint64_t* n_elements);

@@ -100,6 +100,11 @@ SYMBOLS = {
     "ngp_testbed_comm_init": (i32, [vp, vp, u32, u32, C.c_char_p]),
     "ngp_testbed_stats": (i32, [vp, C.POINTER(TrainStats)]),
     "ngp_testbed_n_params": (u64, [vp]),
+    "ngp_testbed_n_encoding_params": (u64, [vp]),
+    "ngp_json_to_msgpack": (i32, [cp, vp, u64, C.POINTER(u64)]),
+    "ngp_msgpack_roundtrip": (i32, [vp, u64, vp, u64, C.POINTER(u64)]),
+    "ngp_testbed_save_snapshot": (i32, [vp, vp, cp, C.c_int32, C.c_int32]),
+    "ngp_testbed_load_snapshot": (i32, [vp, vp, cp]),
     "ngp_testbed_param_buffer": (i32, [vp, i32, C.POINTER(vp), C.POINTER(u64)]),
     "ngp_testbed_density_grid": (i32, [vp, i32, C.POINTER(vp), C.POINTER(u64)]),
     "ngp_testbed_render": (i32, [vp, vp, vp, vp, vp, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, vp, C.c_int32, vp]),

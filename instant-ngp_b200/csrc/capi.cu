@@ -2,6 +2,7 @@
 // caught, stored per thread and reported as a non-zero status + ngp_last_error().
 #include "../../include/ngp_b200.h"
 #include "testbed.h"
+#include "msgpack_mini.h"
 #include <cstring>
 
 namespace ngp { std::atomic<uint64_t> g_launch_count{0}; }
@@ -252,6 +253,33 @@ int ngp_testbed_stats(ngp_testbed_t t, ngp_train_stats* out) {
     NGP_API_END
 }
 uint64_t ngp_testbed_n_params(ngp_testbed_t t) { return t ? t->tb.n_params() : 0; }
+uint64_t ngp_testbed_n_encoding_params(ngp_testbed_t t) { Trainer* tr = t ? t->tb.trainer() : nullptr; return tr ? tr->n_params - tr->n_matrix_params : 0; }
+int ngp_json_to_msgpack(const char* json, void* out, uint64_t capacity, uint64_t* out_size) {
+    NGP_API_BEGIN NGP_CHECK(json && out_size, "null argument");
+    std::string bytes; msgpack_encode(Json::parse(json), bytes);
+    *out_size = bytes.size();
+    NGP_CHECK(out && bytes.size() <= capacity, "ngp_json_to_msgpack: output buffer too small");
+    memcpy(out, bytes.data(), bytes.size());
+    NGP_API_END
+}
+int ngp_msgpack_roundtrip(const void* in, uint64_t in_size, void* out, uint64_t capacity, uint64_t* out_size) {
+    NGP_API_BEGIN NGP_CHECK(in && out_size, "null argument");
+    std::string bytes; msgpack_encode(msgpack_decode(in, in_size), bytes);
+    *out_size = bytes.size();
+    NGP_CHECK(out && bytes.size() <= capacity, "ngp_msgpack_roundtrip: output buffer too small");
+    memcpy(out, bytes.data(), bytes.size());
+    NGP_API_END
+}
+int ngp_testbed_save_snapshot(ngp_testbed_t t, void* stream, const char* path, int32_t include_optimizer_state, int32_t compress) {
+    NGP_API_BEGIN require_device(); NGP_CHECK(t && path, "null argument");
+    t->tb.save_snapshot(S(stream), path, include_optimizer_state != 0, compress != 0);
+    NGP_API_END
+}
+int ngp_testbed_load_snapshot(ngp_testbed_t t, void* stream, const char* path) {
+    NGP_API_BEGIN require_device(); NGP_CHECK(t && path, "null argument");
+    t->tb.load_snapshot(S(stream), path);
+    NGP_API_END
+}
 int ngp_testbed_param_buffer(ngp_testbed_t t, int which, void** ptr, uint64_t* n) {
     NGP_API_BEGIN NGP_CHECK(t && ptr && n, "null argument");
     Trainer* tr = t->tb.trainer(); NGP_CHECK(tr, "no network loaded");

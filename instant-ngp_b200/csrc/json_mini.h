@@ -1,7 +1,8 @@
 // Minimal JSON reader for the tcnn-style network configs (configs/<mode>/*.json in the reference): objects, arrays,
 // strings, numbers, booleans, null, with // and /* */ comments allowed (the reference parses with
 // json::parse(..., allow_exceptions=true, ignore_comments=true), testbed.cu:268) and "parent"-style merge_patch
-// (testbed.cu:95-106) done by the caller via merge_patch().
+// (testbed.cu:95-106) done by the caller via merge_patch().  Binary values (msgpack bin, used by snapshots: msgpack_mini.h)
+// and an integer/float distinction for numbers are carried so that a config read from a snapshot is written back unchanged.
 #pragma once
 #include <map>
 #include <memory>
@@ -9,13 +10,21 @@
 #include <vector>
 #include <stdexcept>
 #include <cstdlib>
+#include <cstdint>
 #include <cctype>
 
 namespace ngp {
 
 struct Json {
-    enum Type { Null, Bool, Number, String, Array, Object } type = Null;
-    bool b = false; double num = 0; std::string str;
+    enum Type { Null, Bool, Number, String, Array, Object, Binary } type = Null;
+    bool b = false; double num = 0; bool is_float = false; std::string str;   // str also holds the bytes of a Binary
+    Json() = default;
+    static Json number(double v, bool as_float = true) { Json j; j.type = Number; j.num = v; j.is_float = as_float; return j; }
+    static Json integer(int64_t v) { return number((double)v, false); }
+    static Json string(const std::string& v) { Json j; j.type = String; j.str = v; return j; }
+    static Json boolean(bool v) { Json j; j.type = Bool; j.b = v; return j; }
+    static Json binary(const void* p, size_t n) { Json j; j.type = Binary; j.str.assign((const char*)p, n); return j; }
+    static Json array_of(const float* v, size_t n) { Json j; j.type = Array; for (size_t i = 0; i < n; ++i) j.arr.push_back(number(v[i])); return j; }
     std::vector<Json> arr; std::map<std::string, Json> obj;
 
     bool is_object() const { return type == Object; }
@@ -104,7 +113,7 @@ private:
             const char* start = s.c_str() + i; char* end = nullptr;
             j.num = std::strtod(start, &end);
             if (end == start) fail(s, i, "unexpected token");
-            j.type = Number; i += (size_t)(end - start);
+            j.type = Number; j.is_float = std::string(start, (size_t)(end - start)).find_first_of(".eEnN") != std::string::npos; i += (size_t)(end - start);
         }
         return j;
     }

@@ -106,7 +106,14 @@ void Testbed::set_nerf_dataset(cudaStream_t s, uint32_t n_images, const HostImag
     ImageMeta* md = m_metas.get<ImageMeta>(n_images);
     NGP_CUDA_CHECK(cudaMemcpyAsync(md, metas.data(), n_images * sizeof(ImageMeta), cudaMemcpyHostToDevice, s));
     NGP_CUDA_CHECK(cudaStreamSynchronize(s));
-    m_n_images = n_images; m_aabb_scale = aabb_scale;
+    m_n_images = n_images; m_host_metas = metas;
+    load_nerf_post(s, aabb_scale);
+}
+
+// load_nerf_post (testbed_nerf.cu:3046-3112): aabb, cascades, cone angle; occupancy-grid buffers
+void Testbed::load_nerf_post(cudaStream_t s, int aabb_scale) {
+    NGP_CHECK(aabb_scale >= 1, "aabb_scale must be at least 1");
+    m_aabb_scale = aabb_scale;
     const float half = 0.5f * (float)std::min(1 << (NERF_CASCADES - 1), aabb_scale);   // m_aabb.inflate(0.5 * aabb_scale) around 0.5
     for (int k = 0; k < 3; ++k) { aabb.min[k] = 0.5f - half; aabb.max[k] = 0.5f + half; }
     render_aabb = aabb;

@@ -61,6 +61,10 @@ public:
     void render(cudaStream_t s, const float* camera_matrix, const float* focal_length, const float* screen_center, int w, int h, int spp, int y0, int y1,
                 float* rgba_out, bool out_is_device, float* depth_out);
     float compute_image_mse(cudaStream_t s, bool quantize);   // testbed_image.cu:465-527
+    // save_snapshot / load_snapshot (testbed.cu:4873-5057): the network config plus a "snapshot" object (fp16 inference parameters,
+    // fp16 density grid, counters, optionally the optimizer state) as MessagePack; ".ingp" = the same inside a zlib stream
+    void save_snapshot(cudaStream_t s, const std::string& path, bool include_optimizer_state, bool compress);
+    void load_snapshot(cudaStream_t s, const std::string& path);
 
     TrainStats stats() const;
     Trainer* trainer() { return m_trainer.get(); }
@@ -88,6 +92,7 @@ public:
 
 private:
     void reset_network();
+    void load_nerf_post(cudaStream_t s, int aabb_scale);                                           // testbed_nerf.cu:3046-3112
     void training_prep_nerf(cudaStream_t s);                                                       // testbed_nerf.cu:4137-4152
     void update_density_grid_nerf(cudaStream_t s, float decay, uint32_t n_uniform, uint32_t n_nonuniform);   // :3412-3536
     void train_nerf_step(cudaStream_t s, uint32_t target_batch_size);                              // :3867-4132
@@ -117,7 +122,7 @@ private:
 
     // NeRF dataset + occupancy grid
     uint32_t m_n_images = 0; int m_aabb_scale = 1; uint32_t m_max_cascade = 0;
-    std::vector<void*> m_image_buffers; std::vector<size_t> m_image_bytes; DeviceBuffer m_metas;
+    std::vector<void*> m_image_buffers; std::vector<size_t> m_image_bytes; DeviceBuffer m_metas; std::vector<ImageMeta> m_host_metas;
     DeviceBuffer m_density_grid, m_density_grid_tmp, m_bitfield, m_mean, m_partials, m_grid_pos, m_grid_idx, m_grid_out;
     uint32_t m_density_grid_ema_step = 0; bool m_grid_allocated = false;
     // NerfCounters (testbed.h:433-447)

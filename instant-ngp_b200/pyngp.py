@@ -159,6 +159,26 @@ class Testbed:
     def n_params(self):
         return lib().ngp_testbed_n_params(self._h)
 
+    def n_encoding_params(self):
+        return lib().ngp_testbed_n_encoding_params(self._h)
+
+    # ---- snapshots (python_api.cu:446-449) ----
+    def save_snapshot(self, path, include_optimizer_state=False, compress=True):
+        check(lib().ngp_testbed_save_snapshot(self._h, _stream(), os.fspath(path).encode(), int(include_optimizer_state), int(compress)))
+
+    def load_snapshot(self, path):
+        check(lib().ngp_testbed_load_snapshot(self._h, _stream(), os.fspath(path).encode()))
+
+    def load_file(self, path):
+        """Testbed::load_file (testbed.cu:316-370): snapshots by extension, .json as a network config."""
+        p = os.fspath(path)
+        if p.lower().endswith((".ingp", ".msgpack")):
+            self.load_snapshot(p)
+        elif p.lower().endswith(".json"):
+            self.reload_network_from_file(p)
+        else:
+            raise RuntimeError(f"File '{p}' is not a snapshot or network config")
+
     # ---- training ----
     def enable_data_parallel(self, process_group=None, native=None):
         """Shard training rays over the ranks of a torch.distributed process group (collective: every rank calls it).
