@@ -143,6 +143,24 @@ void ngp_testbed_destroy(ngp_testbed_t t);
 int ngp_testbed_reload_network_from_json(ngp_testbed_t t, const char* json);            /* python_api.cu:402-407 */
 /* load_training_data (python_api.cu:398) with in-memory views; uploads pixels host->device */
 int ngp_testbed_set_nerf_dataset(ngp_testbed_t t, void* stream, uint32_t n_images, const ngp_training_image* images, int32_t aabb_scale);
+/* load_training_data(path) for a NeRF scene (python_api.cu:398; load_nerf, src/nerf_loader.cu:259-726): the host side of the loader.
+ * ngp_nerf_dataset_open parses one or more transforms.json files (paths separated by '\n') and does everything load_nerf derives
+ * from them: natural-order frame sort, n_frames / sharpness culling, scene scale / offset / aabb / aabb_scale / up, per-frame
+ * lens + principal point + NeRF -> NGP pose.  Decoding the image files is the caller's job (the reference uses stb_image, a
+ * third-party dependency): for each frame i read ngp_nerf_dataset_image_path, decode, and hand the pixels ([h][w][4] uint8 sRGB
+ * straight alpha = data_type 0, or float32 = 1) to ngp_nerf_dataset_set_image, which also resolves the focal length (the fov
+ * forms need the resolution).  ngp_testbed_load_nerf_dataset then uploads the views (= set_nerf_dataset with the file's aabb_scale). */
+typedef struct ngp_nerf_dataset* ngp_nerf_dataset_t;
+int ngp_nerf_dataset_open(const char* json_paths, ngp_nerf_dataset_t* out);
+void ngp_nerf_dataset_close(ngp_nerf_dataset_t d);
+uint32_t ngp_nerf_dataset_n_images(ngp_nerf_dataset_t d);
+int ngp_nerf_dataset_image_path(ngp_nerf_dataset_t d, uint32_t i, char* buf, uint64_t buf_size);
+int ngp_nerf_dataset_set_image(ngp_nerf_dataset_t d, uint32_t i, const void* host_pixels, int32_t data_type, int32_t width, int32_t height);
+/* scene-level results: aabb_scale, scale, offset[3], from_mitsuba */
+int ngp_nerf_dataset_info(ngp_nerf_dataset_t d, int32_t* aabb_scale, float* scale, float* offset3, int32_t* from_mitsuba);
+/* view i as it will be uploaded (pixels point into the dataset's own copy; focal length valid after set_image) */
+int ngp_nerf_dataset_view(ngp_nerf_dataset_t d, uint32_t i, ngp_training_image* out);
+int ngp_testbed_load_nerf_dataset(ngp_testbed_t t, void* stream, ngp_nerf_dataset_t d);
 /* nerf.training.set_image(frame_idx, img) (python_api.cu:49-67,583): replace one view's pixels (same size and type as
  * given to set_nerf_dataset) from HOST memory.  The copy is ordered after everything already queued on `stream` and before the
  * next training step's loss kernel; RGBA8 views travel on an internal copy stream so that the upload runs beside the start of

@@ -88,6 +88,14 @@ SYMBOLS = {
     "ngp_testbed_destroy": (None, [vp]),
     "ngp_testbed_reload_network_from_json": (i32, [vp, cp]),
     "ngp_testbed_set_nerf_dataset": (i32, [vp, vp, u32, vp, C.c_int32]),
+    "ngp_nerf_dataset_open": (i32, [cp, C.POINTER(vp)]),
+    "ngp_nerf_dataset_close": (None, [vp]),
+    "ngp_nerf_dataset_n_images": (u32, [vp]),
+    "ngp_nerf_dataset_image_path": (i32, [vp, u32, cp, u64]),
+    "ngp_nerf_dataset_set_image": (i32, [vp, u32, vp, C.c_int32, C.c_int32, C.c_int32]),
+    "ngp_nerf_dataset_info": (i32, [vp, C.POINTER(C.c_int32), C.POINTER(f32), C.POINTER(f32), C.POINTER(C.c_int32)]),
+    "ngp_nerf_dataset_view": (i32, [vp, u32, C.POINTER(TrainingImage)]),
+    "ngp_testbed_load_nerf_dataset": (i32, [vp, vp, vp]),
     "ngp_testbed_set_training_image": (i32, [vp, vp, u32, vp]),
     "ngp_testbed_set_image": (i32, [vp, vp, vp, C.c_int32, C.c_int32]),
     "ngp_testbed_override_sdf_training_data": (i32, [vp, vp, vp, vp, u32, vp, vp, f32]),

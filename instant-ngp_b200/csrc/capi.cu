@@ -3,6 +3,7 @@
 #include "../../include/ngp_b200.h"
 #include "testbed.h"
 #include "msgpack_mini.h"
+#include "nerf_dataset.h"
 #include <cstring>
 
 namespace ngp { std::atomic<uint64_t> g_launch_count{0}; }
@@ -19,6 +20,7 @@ using namespace ngp;
 
 struct ngp_encoding { GridLayout g; };
 struct ngp_nerf_network { NerfNetwork net; explicit ngp_nerf_network(const Json& j) : net(j) {} };
+struct ngp_nerf_dataset { NerfDataset ds; explicit ngp_nerf_dataset(const std::vector<std::string>& p) : ds(p) {} };
 struct ngp_encoded_mlp { EncodedMlp net; ngp_encoded_mlp(const Json& j, uint32_t i, uint32_t o) : net(j, i, o) {} };
 
 static inline cudaStream_t S(void* s) { return reinterpret_cast<cudaStream_t>(s); }
@@ -193,6 +195,52 @@ int ngp_testbed_set_nerf_dataset(ngp_testbed_t t, void* stream, uint32_t n_image
     NGP_API_BEGIN require_device(); NGP_CHECK(t && images, "null argument");
     static_assert(sizeof(ngp_training_image) == sizeof(HostImage), "ABI struct mismatch");
     t->tb.set_nerf_dataset(S(stream), n_images, reinterpret_cast<const HostImage*>(images), aabb_scale);
+    NGP_API_END
+}
+int ngp_nerf_dataset_open(const char* json_paths, ngp_nerf_dataset_t* out) {
+    NGP_API_BEGIN NGP_CHECK(json_paths && out, "null argument");
+    std::vector<std::string> paths; std::string cur;
+    for (const char* c = json_paths;; ++c) { if (*c == '\n' || *c == 0) { if (!cur.empty()) paths.push_back(cur); cur.clear(); if (!*c) break; } else cur += *c; }
+    *out = new ngp_nerf_dataset(paths);
+    NGP_API_END
+}
+void ngp_nerf_dataset_close(ngp_nerf_dataset_t d) { delete d; }
+uint32_t ngp_nerf_dataset_n_images(ngp_nerf_dataset_t d) { return d ? (uint32_t)d->ds.n_images() : 0; }
+int ngp_nerf_dataset_image_path(ngp_nerf_dataset_t d, uint32_t i, char* buf, uint64_t buf_size) {
+    NGP_API_BEGIN NGP_CHECK(d && buf, "null argument"); NGP_CHECK(i < d->ds.n_images(), "Invalid frame index");
+    const std::string& p = d->ds.frames[i].resolved_path;
+    NGP_CHECK(p.size() + 1 <= buf_size, "image path buffer too small");
+    memcpy(buf, p.c_str(), p.size() + 1);
+    NGP_API_END
+}
+int ngp_nerf_dataset_set_image(ngp_nerf_dataset_t d, uint32_t i, const void* pixels, int32_t data_type, int32_t w, int32_t h) {
+    NGP_API_BEGIN NGP_CHECK(d, "null argument");
+    d->ds.set_image(i, pixels, data_type, w, h);
+    NGP_API_END
+}
+int ngp_nerf_dataset_info(ngp_nerf_dataset_t d, int32_t* aabb_scale, float* scale, float* offset3, int32_t* from_mitsuba) {
+    NGP_API_BEGIN NGP_CHECK(d, "null argument");
+    if (aabb_scale) *aabb_scale = d->ds.aabb_scale; if (scale) *scale = d->ds.scale;
+    if (offset3) memcpy(offset3, d->ds.offset, 12); if (from_mitsuba) *from_mitsuba = d->ds.from_mitsuba;
+    NGP_API_END
+}
+static void fill_view(const DatasetFrame& f, ngp_training_image* o) {
+    o->pixels = f.pixels.empty() ? nullptr : f.pixels.data(); o->data_type = f.data_type; o->res[0] = f.res[0]; o->res[1] = f.res[1];
+    memcpy(o->focal_length, f.focal_length, 8); memcpy(o->principal_point, f.principal_point, 8);
+    o->lens_mode = f.lens_mode; memcpy(o->lens_params, f.lens_params, 16); memcpy(o->xform, f.xform, 48);
+}
+int ngp_nerf_dataset_view(ngp_nerf_dataset_t d, uint32_t i, ngp_training_image* out) {
+    NGP_API_BEGIN NGP_CHECK(d && out, "null argument"); NGP_CHECK(i < d->ds.n_images(), "Invalid frame index");
+    fill_view(d->ds.frames[i], out);
+    NGP_API_END
+}
+int ngp_testbed_load_nerf_dataset(ngp_testbed_t t, void* stream, ngp_nerf_dataset_t d) {
+    NGP_API_BEGIN require_device(); NGP_CHECK(t && d, "null argument");
+    NGP_CHECK(d->ds.complete(), "load_nerf_dataset: every frame needs its decoded pixels first (ngp_nerf_dataset_set_image)");
+    std::vector<ngp_training_image> views(d->ds.n_images());
+    for (size_t i = 0; i < views.size(); ++i) fill_view(d->ds.frames[i], &views[i]);
+    static_assert(sizeof(ngp_training_image) == sizeof(HostImage), "ABI struct drift");
+    t->tb.set_nerf_dataset(S(stream), (uint32_t)views.size(), reinterpret_cast<const HostImage*>(views.data()), d->ds.aabb_scale);
     NGP_API_END
 }
 int ngp_testbed_set_training_image(ngp_testbed_t t, void* stream, uint32_t frame_idx, const void* pixels_host) {

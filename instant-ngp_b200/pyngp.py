@@ -123,6 +123,44 @@ class Testbed:
         check(lib().ngp_testbed_set_nerf_dataset(self._h, _stream(), len(views), arr, int(aabb_scale)))
         self._keep.clear()
 
+    def load_training_data(self, path):
+        """Testbed.load_training_data(path) (python_api.cu:398) for a NeRF scene: `path` is a transforms.json, a directory holding
+        *.json files, or a list of either.  The loader logic (frame order, culling, intrinsics, NeRF -> NGP poses) runs in the
+        library (csrc/nerf_dataset.cu); this binding only decodes the image files it names (OpenCV: png / jpg / exr ...)."""
+        if self.mode != TestbedMode.Nerf:
+            raise RuntimeError("load_training_data: implemented for the Nerf mode (Image: set_image, Sdf: override_sdf_training_data)")
+        import cv2
+        paths = []
+        for p in ([path] if isinstance(path, (str, os.PathLike)) else list(path)):
+            p = os.fspath(p)
+            if os.path.isdir(p):
+                paths += sorted(os.path.join(p, f) for f in os.listdir(p) if f.lower().endswith(".json"))
+            else:
+                paths.append(p)
+        d = C.c_void_p()
+        check(lib().ngp_nerf_dataset_open("\n".join(paths).encode(), C.byref(d)))
+        try:
+            buf = C.create_string_buffer(4096)
+            for i in range(lib().ngp_nerf_dataset_n_images(d)):
+                check(lib().ngp_nerf_dataset_image_path(d, i, buf, 4096))
+                f = buf.value.decode()
+                img = cv2.imread(f, cv2.IMREAD_UNCHANGED)
+                if img is None:
+                    raise RuntimeError(f"Could not find image file '{f}'.")
+                if img.ndim == 2:
+                    img = np.repeat(img[..., None], 3, axis=2)
+                is_float = img.dtype == np.float32
+                if img.dtype == np.uint16:
+                    img = (img >> 8).astype(np.uint8)
+                if img.shape[2] == 3:      # stb_image with 4 requested components: opaque alpha
+                    alpha = np.full(img.shape[:2] + (1,), 1.0 if is_float else 255, img.dtype)
+                    img = np.concatenate([img, alpha], axis=2)
+                img = np.ascontiguousarray(img[..., [2, 1, 0, 3]])          # BGRA -> RGBA
+                check(lib().ngp_nerf_dataset_set_image(d, i, img.ctypes.data_as(C.c_void_p), int(is_float), img.shape[1], img.shape[0]))
+            check(lib().ngp_testbed_load_nerf_dataset(self._h, _stream(), d))
+        finally:
+            lib().ngp_nerf_dataset_close(d)
+
     def set_training_image(self, frame_idx, pixels):
         """nerf.training.set_image(frame_idx, img) (python_api.cu:49-67): host pixels -> the device copy of one view."""
         if isinstance(pixels, torch.Tensor):
