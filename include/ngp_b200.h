@@ -217,6 +217,12 @@ int ngp_testbed_density_grid(ngp_testbed_t t, int which, void** dev_ptr, uint64_
  * averaged over spp; camera = mat4x3 column major; out is a HOST buffer unless out_is_device */
 int ngp_testbed_render(ngp_testbed_t t, void* stream, const float* camera_matrix, const float* focal_length, const float* screen_center,
                        int32_t width, int32_t height, int32_t spp, int32_t y0, int32_t y1, float* rgba_out, int32_t out_is_device, float* depth_out);
+/* nerf.render_lens / render_with_lens_distortion (set_camera_to_training_view): lens model applied to the rays of
+ * ngp_testbed_render; lens_mode 0 Perspective, 1 OpenCV (k1, k2, p1, p2) */
+int ngp_testbed_set_render_lens(ngp_testbed_t t, int32_t lens_mode, const float* lens_params4);
+/* metadata of training view i as loaded (nerf.training.dataset.metadata[i] + xforms[i]); pixels is the DEVICE copy */
+int ngp_testbed_training_view(ngp_testbed_t t, uint32_t i, ngp_training_image* out);
+uint32_t ngp_testbed_n_training_views(ngp_testbed_t t);
 int ngp_testbed_compute_image_mse(ngp_testbed_t t, void* stream, int32_t quantize_to_byte, float* mse_out);   /* python_api.cu:444 */
 /* runtime knobs (pyngp def_readwrite members, python_api.cu:452-537,611-695); value semantics per name:
  * "random_bg_color","linear_colors","snap_to_pixel_centers","shall_train_encoding","shall_train_network" (bool),

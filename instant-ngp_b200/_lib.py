@@ -116,6 +116,9 @@ SYMBOLS = {
     "ngp_testbed_param_buffer": (i32, [vp, i32, C.POINTER(vp), C.POINTER(u64)]),
     "ngp_testbed_density_grid": (i32, [vp, i32, C.POINTER(vp), C.POINTER(u64)]),
     "ngp_testbed_render": (i32, [vp, vp, vp, vp, vp, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, vp, C.c_int32, vp]),
+    "ngp_testbed_set_render_lens": (i32, [vp, C.c_int32, vp]),
+    "ngp_testbed_training_view": (i32, [vp, u32, C.POINTER(TrainingImage)]),
+    "ngp_testbed_n_training_views": (u32, [vp]),
     "ngp_testbed_compute_image_mse": (i32, [vp, vp, C.c_int32, C.POINTER(f32)]),
     "ngp_testbed_set_option": (i32, [vp, cp, C.c_double]),
     "ngp_testbed_get_option": (i32, [vp, cp, C.POINTER(C.c_double)]),

@@ -349,6 +349,22 @@ int ngp_testbed_render(ngp_testbed_t t, void* stream, const float* cam, const fl
     t->tb.render(S(stream), cam, focal, center, w, h, spp, y0, y1, out, out_is_device != 0, depth);
     NGP_API_END
 }
+int ngp_testbed_set_render_lens(ngp_testbed_t t, int32_t lens_mode, const float* p) {
+    NGP_API_BEGIN NGP_CHECK(t, "null argument");
+    NGP_CHECK(lens_mode == LENS_PERSPECTIVE || (lens_mode == LENS_OPENCV && p), "render lens must be Perspective (0) or OpenCV (1) with 4 parameters");
+    t->tb.render_lens_mode = lens_mode;
+    for (int k = 0; k < 4; ++k) t->tb.render_lens_params[k] = (lens_mode == LENS_OPENCV) ? p[k] : 0.f;
+    NGP_API_END
+}
+uint32_t ngp_testbed_n_training_views(ngp_testbed_t t) { return t ? (uint32_t)t->tb.training_views().size() : 0; }
+int ngp_testbed_training_view(ngp_testbed_t t, uint32_t i, ngp_training_image* o) {
+    NGP_API_BEGIN NGP_CHECK(t && o, "null argument"); NGP_CHECK(i < t->tb.training_views().size(), "Invalid frame index");
+    const ImageMeta& m = t->tb.training_views()[i];
+    o->pixels = m.pixels; o->data_type = m.data_type; o->res[0] = m.res[0]; o->res[1] = m.res[1];
+    memcpy(o->focal_length, m.focal_length, 8); memcpy(o->principal_point, m.principal_point, 8);
+    o->lens_mode = m.lens_mode; memcpy(o->lens_params, m.lens_params, 16); memcpy(o->xform, m.xform, 48);
+    NGP_API_END
+}
 int ngp_testbed_compute_image_mse(ngp_testbed_t t, void* stream, int32_t quantize, float* out) {
     NGP_API_BEGIN require_device(); NGP_CHECK(t && out, "null argument");
     *out = t->tb.compute_image_mse(S(stream), quantize != 0);

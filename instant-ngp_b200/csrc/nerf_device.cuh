@@ -61,6 +61,34 @@ NGP_HD float from_stepping_space(float n, float cone_angle) {
 NGP_HD float advance_n_steps(float t, float cone_angle, float n) { return from_stepping_space(to_stepping_space(t, cone_angle) + n, cone_angle); }
 NGP_HD float calc_dt(float t, float cone_angle) { return advance_n_steps(t, cone_angle, 1.0f) - t; }
 
+// The same three functions with everything that depends on the cone angle alone evaluated once (the reference recomputes
+// log1p_c, a, b, at, bt — six logf and two expf — inside every call; per marcher step that is ~20 transcendentals on the
+// serial t chain).  Same expressions on the same inputs, hence the same bits; what is left per call is one logf or one expf.
+struct Cone {
+    float angle, log1p_c, a, b, at, bt;
+    NGP_HD explicit Cone(float cone_angle) : angle(cone_angle), log1p_c(0.f), a(0.f), b(0.f), at(0.f), bt(0.f) {
+        if (cone_angle <= 1e-5f) return;
+        log1p_c = logf(1.0f + cone_angle);
+        a = (logf(MIN_CONE_STEPSIZE()) - logf(log1p_c)) / log1p_c;
+        b = (logf(MAX_CONE_STEPSIZE()) - logf(log1p_c)) / log1p_c;
+        at = expf(a * log1p_c); bt = expf(b * log1p_c);
+    }
+};
+NGP_HD float to_stepping_space(float t, const Cone& c) {
+    if (c.angle <= 1e-5f) return t / MIN_CONE_STEPSIZE();
+    if (t <= c.at) return (t - c.at) / MIN_CONE_STEPSIZE() + c.a;
+    else if (t <= c.bt) return logf(t) / c.log1p_c;
+    else return (t - c.bt) / MAX_CONE_STEPSIZE() + c.b;
+}
+NGP_HD float from_stepping_space(float n, const Cone& c) {
+    if (c.angle <= 1e-5f) return n * MIN_CONE_STEPSIZE();
+    if (n <= c.a) return (n - c.a) * MIN_CONE_STEPSIZE() + c.at;
+    else if (n <= c.b) return expf(n * c.log1p_c);
+    else return (n - c.b) * MAX_CONE_STEPSIZE() + c.bt;
+}
+NGP_HD float advance_n_steps(float t, const Cone& c, float n) { return from_stepping_space(to_stepping_space(t, c) + n, c); }
+NGP_HD float calc_dt(float t, const Cone& c) { return advance_n_steps(t, c, 1.0f) - t; }
+
 // ---- occupancy lookup (testbed_nerf.cu:433-457,614-633) ----
 NGP_HD uint32_t mip_from_pos(V3 p, uint32_t max_cascade) {
     int e;
@@ -102,6 +130,14 @@ NGP_HD float distance_to_next_voxel(V3 pos, V3 dir, V3 idir, float res) {
     return fmaxf(t / res, 0.0f);
 }
 NGP_HD float advance_to_next_voxel(float t, float cone, V3 pos, V3 dir, V3 idir, uint32_t mip) {
+    float res = scalbnf((float)NERF_GRIDSIZE, -(int)mip);
+    float t_target = t + distance_to_next_voxel(pos, dir, idir, res);
+    t = to_stepping_space(t, cone);
+    t_target = to_stepping_space(t_target, cone);
+    return from_stepping_space(t + ceilf(fmaxf(t_target - t, 0.5f)), cone);
+}
+
+NGP_HD float advance_to_next_voxel(float t, const Cone& cone, V3 pos, V3 dir, V3 idir, uint32_t mip) {
     float res = scalbnf((float)NERF_GRIDSIZE, -(int)mip);
     float t_target = t + distance_to_next_voxel(pos, dir, idir, res);
     t = to_stepping_space(t, cone);

@@ -296,12 +296,12 @@ NGP_D RayConst make_ray_const(V3 o, V3 d) {
     return {o, d, v3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z), v3(0.5f * copysignf(1.0f, d.x), 0.5f * copysignf(1.0f, d.y), 0.5f * copysignf(1.0f, d.z))};
 }
 template <bool FLAT>
-NGP_D void candidate_dt_mip(float t, V3 pos, float cone, uint32_t max_mip, float& dt, uint32_t& mip, float& n) {
+NGP_D void candidate_dt_mip(float t, V3 pos, const Cone& cone, uint32_t max_mip, float& dt, uint32_t& mip, float& n) {
     if (FLAT) { n = div_by_stepsize(t); dt = (n + 1.0f) * MIN_CONE_STEPSIZE() - t; mip = 0; }
     else { n = 0.f; dt = calc_dt(t, cone); mip = mip_from_dt(dt, pos, max_mip); }
 }
 template <bool FLAT>
-NGP_D float candidate_skip(float t, float n, V3 pos, const RayConst& r, float cone, uint32_t mip) {
+NGP_D float candidate_skip(float t, float n, V3 pos, const RayConst& r, const Cone& cone, uint32_t mip) {
     if (FLAT) {
         const V3 p = (float)NERF_GRIDSIZE * (pos - v3(0.5f, 0.5f, 0.5f));
         const float tx = (floorf(p.x + 0.5f + r.hs.x) - p.x) * r.idir.x;
@@ -315,7 +315,7 @@ NGP_D float candidate_skip(float t, float n, V3 pos, const RayConst& r, float co
 }
 
 template <bool WRITE>
-NGP_D uint32_t march_training_ray(V3 o, V3 d, float startt, float cone, const Aabb& aabb, const uint8_t* __restrict__ bitfield, uint32_t max_mip,
+NGP_D uint32_t march_training_ray(V3 o, V3 d, float startt, const Cone& cone, const Aabb& aabb, const uint8_t* __restrict__ bitfield, uint32_t max_mip,
                                   uint32_t limit, float* __restrict__ coords) {
     const V3 idir = v3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
     const V3 wd = warp_direction(d);
@@ -342,7 +342,7 @@ NGP_D uint32_t march_training_ray(V3 o, V3 d, float startt, float cone, const Aa
 // the K occupancy bytes are fetched as independent loads (one exposed L2 latency per K candidates instead of one per
 // candidate), then resolved in order.  No redundant chain work, no cross-lane traffic; bit-identical by construction.
 template <bool WRITE, bool FLAT, uint32_t K>
-NGP_D uint32_t march_training_ray_ilp(V3 o, V3 d, float startt, float cone, const Aabb& aabb, const uint8_t* __restrict__ bitfield, uint32_t max_mip,
+NGP_D uint32_t march_training_ray_ilp(V3 o, V3 d, float startt, const Cone& cone, const Aabb& aabb, const uint8_t* __restrict__ bitfield, uint32_t max_mip,
                                       uint32_t limit, float* __restrict__ coords, SampleLog* log = nullptr) {
     if (limit == 0) return 0;
     const RayConst rc = make_ray_const(o, d);
@@ -436,14 +436,14 @@ __global__ void __launch_bounds__(SCAN_BLOCK) sampler_count_kernel(uint32_t n_ra
             if (du.x == 0.f && du.y == 0.f && du.z == 0.f) { o = v3(m.xform[9], m.xform[10], m.xform[11]); du = v3(m.xform[6], m.xform[7], m.xform[8]); }
             const V3 d = normalize3(du);
             float tmin, tmax; aabb_ray_intersect(aabb, o, d, tmin, tmax);
-            const float cone = cone_angle_constant;   // calc_cone_angle (:114-122)
+            const Cone cone(cone_angle_constant);   // calc_cone_angle (:114-122)
             tmin = fmaxf(tmin, 0.0f);
             const float startt = advance_n_steps(tmin, cone, rng.next_float());
             SampleLog log{b.sample_scratch + (size_t)i * b.scratch_per_ray, b.scratch_per_ray, b.sample_pool, b.pool_slots, &b.counters[3], NO_SLOT};
             numsteps = march_training_ray_ilp<false, FLAT, ILP_K>(o, d, startt, cone, aabb, bitfield, max_mip, NERF_STEPS, nullptr, &log);
             b.overflow_slot[i] = log.slot;
             float* rt = b.ray_tmp + (size_t)i * 8;
-            rt[0] = o.x; rt[1] = o.y; rt[2] = o.z; rt[3] = du.x; rt[4] = du.y; rt[5] = du.z; rt[6] = startt; rt[7] = cone;
+            rt[0] = o.x; rt[1] = o.y; rt[2] = o.z; rt[3] = du.x; rt[4] = du.y; rt[5] = du.z; rt[6] = startt; rt[7] = cone.angle;
         }
         b.numsteps_all[i] = numsteps;
     }
@@ -486,7 +486,7 @@ __global__ void __launch_bounds__(SCAN_BLOCK) sampler_write_kernel(uint32_t n_ra
         }
         return;
     }
-    march_training_ray_ilp<true, FLAT, ILP_K>(o, d, rt[6], rt[7], aabb, bitfield, max_mip, numsteps, coords);
+    march_training_ray_ilp<true, FLAT, ILP_K>(o, d, rt[6], Cone(rt[7]), aabb, bitfield, max_mip, numsteps, coords);
 }
 
 // ---- warp-cooperative marcher: G lanes per ray ------------------------------------------------------------------
@@ -512,7 +512,7 @@ NGP_D float div_by_stepsize_in_range(float t) {
     const float q = t * RS; return fmaf(fmaf(-q, S, t), RS, q);
 }
 template <bool FLAT, bool STEP, bool FAST>
-NGP_D float chain_next(float t, const RayConst& rc, float cone, uint32_t max_mip) {
+NGP_D float chain_next(float t, const RayConst& rc, const Cone& cone, uint32_t max_mip) {
     if (FLAT && FAST) {
         const float n = div_by_stepsize_in_range(t);
         if (STEP) return t + ((n + 1.0f) * MIN_CONE_STEPSIZE() - t);
@@ -532,10 +532,14 @@ NGP_D float chain_next(float t, const RayConst& rc, float cone, uint32_t max_mip
     return STEP ? t + dt : candidate_skip<FLAT>(t, n, pos, rc, cone, mip);
 }
 template <uint32_t G, uint32_t K, bool FLAT, bool STEP, bool FAST>
-NGP_D float chain_round(float t, float* my_t, uint32_t lane, const RayConst& rc, float cone, uint32_t max_mip) {
+NGP_D float chain_round(float t, float* my_t, uint32_t lane, const RayConst& rc, const Cone& cone, uint32_t max_mip) {
+    // general path (cascades / cone angle): one chain step is ~250 instructions (logf, expf, IEEE divisions, frexp); unrolled
+    // eight-fold and instantiated per mode it outgrows the instruction cache, and with ~8 warps per SM nothing hides the misses
+    // (ncu: 73 % of the warp cycles in "no instruction").  The loop stays rolled there.
+    constexpr int UNROLL = FLAT ? (G < 8 ? (int)G : 8) : 1;
 #pragma unroll
     for (uint32_t k = 0; k < K; ++k) {
-#pragma unroll (G < 8 ? G : 8)
+#pragma unroll UNROLL
         for (uint32_t g = 0; g < G; ++g) {
             if (g == lane) my_t[k] = t;
             t = chain_next<FLAT, STEP, FAST>(t, rc, cone, max_mip);
@@ -544,7 +548,7 @@ NGP_D float chain_round(float t, float* my_t, uint32_t lane, const RayConst& rc,
     return t;
 }
 template <uint32_t G, bool WRITE, bool FLAT, uint32_t K = 1>
-NGP_D uint32_t march_training_ray_group(V3 o, V3 d, float startt, float cone, const Aabb& aabb, const uint8_t* __restrict__ bitfield, uint32_t max_mip,
+NGP_D uint32_t march_training_ray_group(V3 o, V3 d, float startt, const Cone& cone, const Aabb& aabb, const uint8_t* __restrict__ bitfield, uint32_t max_mip,
                                         uint32_t limit, float* __restrict__ coords, uint32_t lane, uint32_t gshift, uint32_t gmask, SampleLog* log = nullptr) {
     constexpr uint32_t C = G * K;
     static_assert(C <= 32, "at most 32 candidates per round");
@@ -652,12 +656,12 @@ __global__ void __launch_bounds__(128) sampler_classify_kernel(uint32_t n_rays, 
             if (du.x == 0.f && du.y == 0.f && du.z == 0.f) { o = v3(m.xform[9], m.xform[10], m.xform[11]); du = v3(m.xform[6], m.xform[7], m.xform[8]); }
             const V3 d = normalize3(du);
             float tmin, tmax; aabb_ray_intersect(aabb, o, d, tmin, tmax);
-            const float cone = cone_angle_constant;   // calc_cone_angle (:114-122)
+            const Cone cone(cone_angle_constant);   // calc_cone_angle (:114-122)
             tmin = fmaxf(tmin, 0.0f);
             if (part == 0) {
                 const float startt = advance_n_steps(tmin, cone, rng.next_float());
                 float* rt = b.ray_tmp + (size_t)i * 8;
-                rt[0] = o.x; rt[1] = o.y; rt[2] = o.z; rt[3] = du.x; rt[4] = du.y; rt[5] = du.z; rt[6] = startt; rt[7] = cone;
+                rt[0] = o.x; rt[1] = o.y; rt[2] = o.z; rt[3] = du.x; rt[4] = du.y; rt[5] = du.z; rt[6] = startt; rt[7] = cone.angle;
             }
             candidate = b.coarse == nullptr || ray_touches_coarse(b.coarse, o, d, tmin, tmax, part, Q);
         }
@@ -683,7 +687,7 @@ __global__ void __launch_bounds__(SCAN_BLOCK) sampler_count_group_kernel(uint32_
     const uint32_t i = b.cand_list[c];
     const float* rt = b.ray_tmp + (size_t)i * 8;
     const V3 o = ld3(rt), du = ld3(rt + 3);
-    const float startt = rt[6], cone = rt[7];
+    const float startt = rt[6]; const Cone cone(rt[7]);
     SampleLog log{b.sample_scratch + (size_t)i * b.scratch_per_ray, b.scratch_per_ray, b.sample_pool, b.pool_slots, &b.counters[3], NO_SLOT};
     const uint32_t numsteps = march_training_ray_group<G, false, FLAT, K>(o, normalize3(du), startt, cone, aabb, bitfield, max_mip, NERF_STEPS, nullptr, lane, gshift, gmask, &log);
     if (lane == 0) {
@@ -725,7 +729,7 @@ __global__ void __launch_bounds__(SCAN_BLOCK) sampler_write_group_kernel(uint32_
     const bool logged = keep && (numsteps <= b.scratch_per_ray || slot < b.pool_slots);
     if (!keep || logged) return;
     const float* rt = b.ray_tmp + (size_t)i * 8;
-    march_training_ray_group<G, true, FLAT>(o, normalize3(du), rt[6], rt[7], aabb, bitfield, max_mip, numsteps, b.coords + (size_t)base * 7, lane, gshift, gmask);
+    march_training_ray_group<G, true, FLAT>(o, normalize3(du), rt[6], Cone(rt[7]), aabb, bitfield, max_mip, numsteps, b.coords + (size_t)base * 7, lane, gshift, gmask);
 }
 
 // Log -> NerfCoordinates, one thread per SAMPLE: the owning ray is found by bisection over the (ascending) base offsets of the
@@ -1195,7 +1199,7 @@ void nerf_fill_rollover(cudaStream_t s, uint32_t n_target, const uint32_t* n_inp
 // compact_kernel_nerf (:2198-2226), generate_next_nerf_network_inputs (:948-1022), composite_kernel_nerf (:1024-1230,
 // Shade mode only), shade_kernel_nerf (:2164-2196).
 // =================================================================================================================
-NGP_D float advance_to_occupied(float t, float cone, V3 o, V3 d, V3 idir, const uint8_t* __restrict__ bitfield, uint32_t min_mip, uint32_t max_mip, const Aabb& aabb) {
+NGP_D float advance_to_occupied(float t, const Cone& cone, V3 o, V3 d, V3 idir, const uint8_t* __restrict__ bitfield, uint32_t min_mip, uint32_t max_mip, const Aabb& aabb) {
     while (true) {   // if_unoccupied_advance_to_next_occupied_voxel (:811-845)
         const V3 pos = ray_at(o, d, t);
         if (t >= MAX_DEPTH || !aabb_contains(aabb, pos)) return MAX_DEPTH;
@@ -1207,15 +1211,16 @@ NGP_D float advance_to_occupied(float t, float cone, V3 o, V3 d, V3 idir, const 
 }
 
 __global__ void init_rays_kernel(RenderCamera cam, uint32_t sample_index, bool snap, Aabb render_aabb, const uint8_t* __restrict__ bitfield,
-                                 uint32_t max_mip, float cone, RaysSoa rays, float* __restrict__ frame_rgba, float* __restrict__ frame_depth) {
+                                 uint32_t max_mip, float cone_angle, RaysSoa rays, float* __restrict__ frame_rgba, float* __restrict__ frame_depth) {
+    const Cone cone(cone_angle);
     const uint32_t x = threadIdx.x + blockDim.x * blockIdx.x, yl = threadIdx.y + blockDim.y * blockIdx.y;
     const uint32_t W = cam.res[0], y = cam.y0 + yl;
     if (x >= W || y >= (uint32_t)cam.y1) return;
     const uint32_t local = x + W * yl, idx = x + W * y;
     float off[2]; ld_random_pixel_offset(snap ? 0 : sample_index, off);
     const float u = ((float)x + off[0]) / (float)W, v = ((float)y + off[1]) / (float)cam.res[1];
-    V3 o, d; float no_lens[4] = {0, 0, 0, 0};
-    uv_to_ray(cam.camera, cam.res, cam.focal_length, cam.screen_center, LENS_PERSPECTIVE, no_lens, u, v, o, d);
+    V3 o, d;
+    uv_to_ray(cam.camera, cam.res, cam.focal_length, cam.screen_center, cam.lens_mode, cam.lens_params, u, v, o, d);
     NerfPayload& p = rays.payload[local];
     p.max_weight = 0.0f; p.idx = idx; p.n_steps = 0; p.alive = 0; p.pad = 0;
     p.origin[0] = o.x; p.origin[1] = o.y; p.origin[2] = o.z;
@@ -1261,7 +1266,8 @@ __global__ void __launch_bounds__(SCAN_BLOCK) compact_scatter_kernel(uint32_t n,
 }
 
 __global__ void next_inputs_kernel(uint32_t n_alive, Aabb render_aabb, Aabb train_aabb, RaysSoa rays, float* __restrict__ input, uint32_t n_steps,
-                                   const uint8_t* __restrict__ bitfield, uint32_t max_mip, float cone) {
+                                   const uint8_t* __restrict__ bitfield, uint32_t max_mip, float cone_angle) {
+    const Cone cone(cone_angle);
     const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x;
     if (i >= n_alive) return;
     NerfPayload& p = rays.payload[i];

@@ -79,6 +79,7 @@ struct RaysSoa { float* rgba; float* depth; NerfPayload* payload; };   // rgba [
 struct RenderCamera {
     int res[2]; float focal_length[2]; float screen_center[2]; float camera[12];
     int y0, y1;     // row band rendered by this call (tile sharding); ray index = x + W*(y - y0)
+    int lens_mode; float lens_params[4];   // m_nerf.render_lens (render_with_lens_distortion): Perspective or OpenCV
 };
 void nerf_init_rays(cudaStream_t s, const RenderCamera& cam, uint32_t sample_index, bool snap_to_pixel_centers, Aabb render_aabb,
                     const uint8_t* bitfield, uint32_t max_mip, float cone_angle, RaysSoa rays, float* frame_rgba, float* frame_depth);

@@ -354,7 +354,11 @@ void Testbed::launch_ray_prefetch(cudaStream_t s, uint32_t target) {
     const SamplerKey key = sampler_key(R, max_inference_samples(target), target);
     // start beside the hash-grid backward pass and the optimizer (atomics- and HBM-bound, few issue slots used); the fused MLP
     // backward kernel (latency-bound, 8 warps per SM) loses more from sharing its SMs than the overlap wins
-    NGP_CUDA_CHECK(cudaStreamWaitEvent(m_aux_stream, m_ev_after_mlp, 0));
+    // That holds for the flat marcher (aabb_scale 1: ~65 M warp instructions at 60 % issue utilisation).  The general marcher
+    // (cascades, cone angle) is one long dependent chain per ray at ~2 warps per scheduler: it takes longer than the whole rest
+    // of the step and uses a tenth of the issue slots, so it starts as soon as the counters are known.
+    const bool flat = cone_angle_constant <= 1e-5f && m_max_cascade == 0;
+    if (flat) NGP_CUDA_CHECK(cudaStreamWaitEvent(m_aux_stream, m_ev_after_mlp, 0));
     const SamplerBuffers sb = sampler_buffers(m_aux_stream, set, target, R);
     launch_sampler(m_aux_stream, key, sb);
     NGP_CUDA_CHECK(cudaEventRecord(m_ev_prefetch, m_aux_stream));
@@ -539,6 +543,7 @@ void Testbed::render(cudaStream_t s, const float* camera_matrix, const float* fo
     RenderCamera cam{};
     cam.res[0] = w; cam.res[1] = h; cam.y0 = y0; cam.y1 = y1;
     memcpy(cam.focal_length, focal_length, 8); memcpy(cam.screen_center, screen_center, 8); memcpy(cam.camera, camera_matrix, 48);
+    cam.lens_mode = render_lens_mode; memcpy(cam.lens_params, render_lens_params, 16);
     NGP_CUDA_CHECK(cudaMemsetAsync(accum, 0, (size_t)n_pixels * 16, s));
     for (int sample = 0; sample < spp; ++sample) {
         nerf_init_rays(s, cam, (uint32_t)sample, snap_to_pixel_centers && spp == 1, render_aabb, m_bitfield.as<uint8_t>(), m_max_cascade, cone_angle_constant, rays[0], frame, fdepth);

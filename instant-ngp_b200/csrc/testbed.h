@@ -89,6 +89,8 @@ public:
     bool prefetch_rays = true;
     uint32_t prefetch_hits = 0;   // read-only: steps whose rays came from a prefetch
     Aabb aabb{{0, 0, 0}, {1, 1, 1}}, render_aabb{{0, 0, 0}, {1, 1, 1}};
+    int render_lens_mode = LENS_PERSPECTIVE; float render_lens_params[4] = {0, 0, 0, 0};   // m_nerf.render_lens (set_camera_to_training_view)
+    const std::vector<ImageMeta>& training_views() const { return m_host_metas; }
 
 private:
     void reset_network();

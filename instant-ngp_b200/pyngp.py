@@ -340,6 +340,38 @@ class Testbed:
         check(lib().ngp_testbed_render(self._h, _stream(), cam, fl, sc, width, height, spp, y0, y1, optr, int(dev_out), dptr))
         return (out, depth) if return_depth else out
 
+    def n_training_views(self):
+        return lib().ngp_testbed_n_training_views(self._h)
+
+    def training_view(self, i):
+        """nerf.training.dataset.metadata[i] / xforms[i] as a view dict (no pixels)"""
+        v = TrainingImage()
+        check(lib().ngp_testbed_training_view(self._h, int(i), C.byref(v)))
+        return {"res": tuple(v.res), "focal_length": tuple(v.focal_length), "principal_point": tuple(v.principal_point), "lens_mode": v.lens_mode,
+                "lens_params": tuple(v.lens_params), "xform": np.array(list(v.xform), np.float32), "data_type": v.data_type, "device_pixels": v.pixels}
+
+    def set_render_lens(self, lens_mode=0, lens_params=(0, 0, 0, 0)):
+        check(lib().ngp_testbed_set_render_lens(self._h, int(lens_mode), (C.c_float * 4)(*lens_params)))
+
+    def render_training_view(self, i, spp=1):
+        """set_camera_to_training_view(i) + render at the view's own resolution, with its lens (scripts/run.py:236-240)"""
+        v = self.training_view(i)
+        self.set_render_lens(v["lens_mode"], v["lens_params"])
+        try:
+            return self.render(v["res"][0], v["res"][1], spp, camera_matrix=v["xform"], focal_length=v["focal_length"], screen_center=v["principal_point"])
+        finally:
+            self.set_render_lens(0)
+
+    def training_view_pixels(self, i):
+        """the device copy of training view i as float32 [H,W,4] linear premultiplied RGBA (what render_ground_truth shows)"""
+        v = self.training_view(i)
+        w, h = v["res"]
+        if v["data_type"] == 0:
+            px = _wrap(v["device_pixels"], w * h * 4, torch.uint8).view(h, w, 4).float() / 255.0
+            rgb = torch.where(px[..., :3] <= 0.04045, px[..., :3] / 12.92, ((px[..., :3] + 0.055) / 1.055) ** 2.4) * px[..., 3:4]
+            return torch.cat([rgb, px[..., 3:4]], dim=2)
+        return _wrap(v["device_pixels"], w * h * 4, torch.float32).view(h, w, 4).clone()
+
     def compute_image_mse(self, quantize=False):
         v = C.c_float()
         check(lib().ngp_testbed_compute_image_mse(self._h, _stream(), int(quantize), C.byref(v)))
