@@ -206,21 +206,60 @@ NGP_D void red_add_entry(__half* p, float w, const float* d) {
     else { red_add_h4(p, w * d[0], w * d[1 % F], w * d[2 % F], w * d[3 % F]); red_add_h4(p + 4, w * d[4 % F], w * d[5 % F], w * d[6 % F], w * d[7 % F]); }
 }
 
+// Samples arrive in ray order, so neighbouring lanes of a warp sit in the same cell of the coarser levels (a level-0 cell holds
+// ~100 consecutive samples of a ray, a level-8 cell two or three): their reductions would all go to the same eight table entries
+// and serialise in the L2 atomic units.  Per level the warp looks for runs of consecutive lanes with identical cell coordinates;
+// when there are few runs (agg_max_runs) the eight corner contributions are summed along each run with a segmented shuffle
+// reduction (fp32) and only the first lane of a run issues reductions.  Fine levels (every lane its own cell) take the direct path.
+
+template <uint32_t D, uint32_t F>
+NGP_D void scatter_corners(const LevelCorners<D>& lc, __half* __restrict__ gl, const float (*v)[F]) {
+    constexpr uint32_t NC = 1u << D;
+    if (F <= 4) {
+        // The two corners along x are table neighbours (index ^ 1) whenever the cell's x is even (hashed: the x term enters the
+        // XOR unmultiplied) or the dense index is even: they then go out as ONE vector reduction.  Scattered reductions cost
+        // one LSU slot per lane, so this removes a quarter of them (measured: 0.136 -> 0.106 ms per 2^18 samples).
+#pragma unroll
+        for (uint32_t k = 0; k < NC; k += 2) {
+            const uint32_t ia = lc.index(k), ib = lc.index(k + 1);
+            if ((ia ^ ib) == 1u) {
+                const bool a_hi = ia & 1u;
+                const float* lo = a_hi ? v[k + 1] : v[k]; const float* hi = a_hi ? v[k] : v[k + 1];
+                __half* p = gl + (size_t)(ia & ~1u) * F;
+                if (F == 1) red_add_h2(p, lo[0], hi[0]);
+                else if (F == 2) red_add_h4(p, lo[0], lo[1 % F], hi[0], hi[1 % F]);
+                else red_add_h8(p, lo[0], lo[1 % F], lo[2 % F], lo[3 % F], hi[0], hi[1 % F], hi[2 % F], hi[3 % F]);
+            } else {
+                red_add_entry<F>(gl + (size_t)ia * F, 1.0f, v[k]);
+                red_add_entry<F>(gl + (size_t)ib * F, 1.0f, v[k + 1]);
+            }
+        }
+    } else {
+#pragma unroll
+        for (uint32_t k = 0; k < NC; ++k) red_add_entry<F>(gl + (size_t)lc.index(k) * F, 1.0f, v[k]);
+    }
+}
+
 template <uint32_t D, uint32_t F>
 __global__ void __launch_bounds__(256) grid_backward_kernel(const GridLayout g, const float* __restrict__ x, uint32_t x_stride, uint32_t n,
-                                                            const __half* __restrict__ dy, int dy_layout, __half* __restrict__ grad, uint32_t chunk0) {
+                                                            const __half* __restrict__ dy, int dy_layout, __half* __restrict__ grad, uint32_t chunk0, uint32_t agg_max_runs) {
     constexpr uint32_t LPC = 8 / F;
     constexpr uint32_t NC = 1u << D;
-    const uint32_t row = blockIdx.x * blockDim.x + threadIdx.x, chunk = chunk0 + blockIdx.y;
-    if (row >= n) return;
-    size_t off = (dy_layout == LAYOUT_BLK8) ? blk8_chunk_offset(row, chunk, g.padded_width) : (size_t)row * g.padded_width + chunk * 8;
-    const uint4 raw = __ldg(reinterpret_cast<const uint4*>(dy + off));
-    if ((raw.x | raw.y | raw.z | raw.w) == 0u) return;   // padding rows / untouched levels contribute nothing
-    const __half* dh = reinterpret_cast<const __half*>(&raw);
-    const float* xp = x + (size_t)row * x_stride;
+    const uint32_t row = blockIdx.x * blockDim.x + threadIdx.x, chunk = chunk0 + blockIdx.y, lane = threadIdx.x & 31u;
+    const bool in_range = row < n;
+    uint4 raw = make_uint4(0u, 0u, 0u, 0u);
     float xs[D];
 #pragma unroll
-    for (uint32_t d = 0; d < D; ++d) xs[d] = __ldg(xp + d);
+    for (uint32_t d = 0; d < D; ++d) xs[d] = 0.0f;
+    if (in_range) {
+        const size_t off = (dy_layout == LAYOUT_BLK8) ? blk8_chunk_offset(row, chunk, g.padded_width) : (size_t)row * g.padded_width + chunk * 8;
+        raw = __ldg(reinterpret_cast<const uint4*>(dy + off));
+        const float* xp = x + (size_t)row * x_stride;
+#pragma unroll
+        for (uint32_t d = 0; d < D; ++d) xs[d] = __ldg(xp + d);
+    }
+    if (__ballot_sync(0xffffffffu, (raw.x | raw.y | raw.z | raw.w) != 0u) == 0u) return;   // padding rows / untouched levels contribute nothing
+    const __half* dh = reinterpret_cast<const __half*>(&raw);
 #pragma unroll
     for (uint32_t li = 0; li < LPC; ++li) {
         const uint32_t level = chunk * LPC + li;
@@ -228,32 +267,37 @@ __global__ void __launch_bounds__(256) grid_backward_kernel(const GridLayout g, 
         float d[F]; bool any = false;
 #pragma unroll
         for (uint32_t f = 0; f < F; ++f) { d[f] = __half2float(dh[li * F + f]); any |= d[f] != 0.0f; }
-        if (!any) continue;
+        const uint32_t any_mask = __ballot_sync(0xffffffffu, any);
+        if (any_mask == 0u) continue;
         const LevelCorners<D> lc(g, level, xs);
         __half* gl = grad + (size_t)g.offsets[level] * F;
-        if (F <= 4) {
-            // The two corners along x are table neighbours (index ^ 1) whenever the cell's x is even (hashed: the x term enters the
-            // XOR unmultiplied) or the dense index is even: they then go out as ONE vector reduction.  Scattered reductions cost
-            // one LSU slot per lane, so this removes a quarter of them (measured: 0.136 -> 0.106 ms per 2^18 samples).
+        float v[NC][F];
 #pragma unroll
-            for (uint32_t k = 0; k < NC; k += 2) {
-                const uint32_t ia = lc.index(k), ib = lc.index(k + 1);
-                const float wa = lc.weight(k), wb = lc.weight(k + 1);
-                if ((ia ^ ib) == 1u) {
-                    const bool a_hi = ia & 1u;
-                    const float wl = a_hi ? wb : wa, wh = a_hi ? wa : wb;
-                    __half* p = gl + (size_t)(ia & ~1u) * F;
-                    if (F == 1) red_add_h2(p, wl * d[0], wh * d[0]);
-                    else if (F == 2) red_add_h4(p, wl * d[0], wl * d[1 % F], wh * d[0], wh * d[1 % F]);
-                    else red_add_h8(p, wl * d[0], wl * d[1 % F], wl * d[2 % F], wl * d[3 % F], wh * d[0], wh * d[1 % F], wh * d[2 % F], wh * d[3 % F]);
-                } else {
-                    red_add_entry<F>(gl + (size_t)ia * F, wa, d);
-                    red_add_entry<F>(gl + (size_t)ib * F, wb, d);
-                }
+        for (uint32_t k = 0; k < NC; ++k) {
+            const float w = lc.weight(k);
+#pragma unroll
+            for (uint32_t f = 0; f < F; ++f) v[k][f] = any ? w * d[f] : 0.0f;
+        }
+        // runs of consecutive lanes in the same cell (the per-axis terms identify the cell within a level)
+        bool same = any;
+#pragma unroll
+        for (uint32_t dd = 0; dd < D; ++dd) same &= __shfl_up_sync(0xffffffffu, lc.term[dd][0], 1) == lc.term[dd][0];
+        same &= lane != 0 && ((any_mask >> (lane - 1u)) & 1u);
+        const uint32_t heads = __ballot_sync(0xffffffffu, !same);
+        if ((uint32_t)__popc(heads) <= agg_max_runs) {
+            const uint32_t above = lane == 31u ? 0u : (heads & (0xffffffffu << (lane + 1u)));
+            const uint32_t run_end = above ? (uint32_t)__ffs((int)above) - 2u : 31u;      // last lane of this lane's run
+#pragma unroll
+            for (uint32_t o = 1; o < 32; o <<= 1) {
+                const bool take = lane + o <= run_end;
+#pragma unroll
+                for (uint32_t k = 0; k < NC; ++k)
+#pragma unroll
+                    for (uint32_t f = 0; f < F; ++f) { const float t = __shfl_down_sync(0xffffffffu, v[k][f], o); if (take) v[k][f] += t; }
             }
-        } else {
-#pragma unroll
-            for (uint32_t k = 0; k < NC; ++k) red_add_entry<F>(gl + (size_t)lc.index(k) * F, lc.weight(k), d);
+            if (!same && any) scatter_corners<D, F>(lc, gl, v);
+        } else if (any) {
+            scatter_corners<D, F>(lc, gl, v);
         }
     }
 }
@@ -350,12 +394,19 @@ void grid_forward(cudaStream_t s, const GridLayout& g, const __half* table, cons
     GRID_DISPATCH(grid_forward_kernel, g, table, x, x_stride, n, y, y_layout);
 }
 
+// runs per warp up to which a level is aggregated (0 = never); NGP_AGG_MAX_RUNS overrides for experiments.  Measured (tools/sweep_agg.sh,
+// grid_backward ms per 2^18 samples, synthetic scene / fox): 0: 0.119 / 0.359, 4: 0.109 / 0.216, 8: 0.113 / 0.184, 12: 0.108 / 0.163, 16: 0.126 / 0.141
+static uint32_t agg_max_runs() {
+    static const uint32_t v = [] { const char* e = getenv("NGP_AGG_MAX_RUNS"); return e ? (uint32_t)atoi(e) : 12u; }();
+    return v;
+}
+
 void grid_backward(cudaStream_t s, const GridLayout& g, const float* x, uint32_t x_stride, uint32_t n, const __half* dy,
                    int dy_layout, __half* grad) {
     if (n == 0) return;
     NGP_PROFILE_SCOPE(s, "grid_backward", n);
     const dim3 blocks(div_round_up(n, 256), g.padded_width / 8, 1);
-    GRID_DISPATCH(grid_backward_kernel, g, x, x_stride, n, dy, dy_layout, grad, 0u);
+    GRID_DISPATCH(grid_backward_kernel, g, x, x_stride, n, dy, dy_layout, grad, 0u, agg_max_runs());
 }
 
 // the same pass restricted to 8-feature chunks [chunk0, chunk0 + n_chunks): the data-parallel step launches it chunk by chunk
@@ -365,7 +416,7 @@ void grid_backward_chunks(cudaStream_t s, const GridLayout& g, const float* x, u
     if (n == 0 || n_chunks == 0) return;
     NGP_PROFILE_SCOPE(s, "grid_backward", n);
     const dim3 blocks(div_round_up(n, 256), n_chunks, 1);
-    GRID_DISPATCH(grid_backward_kernel, g, x, x_stride, n, dy, dy_layout, grad, chunk0);
+    GRID_DISPATCH(grid_backward_kernel, g, x, x_stride, n, dy, dy_layout, grad, chunk0, agg_max_runs());
 }
 
 void grid_backward_input(cudaStream_t s, const GridLayout& g, const __half* table, const float* x, uint32_t x_stride,
