@@ -90,25 +90,46 @@ NGP_HD float advance_n_steps(float t, const Cone& c, float n) { return from_step
 NGP_HD float calc_dt(float t, const Cone& c) { return advance_n_steps(t, c, 1.0f) - t; }
 
 // ---- occupancy lookup (testbed_nerf.cu:433-457,614-633) ----
+// frexpf / scalbnf on the values this file feeds them, without the library's range handling: the exponent field read or
+// written directly (exact for normal numbers; zero, denormals, inf and nan take the library call, so the result is the same
+// for every input).
+NGP_HD int float_bits(float x) {
+#ifdef __CUDA_ARCH__
+    return __float_as_int(x);
+#else
+    int i; memcpy(&i, &x, 4); return i;
+#endif
+}
+NGP_HD float bits_float(int i) {
+#ifdef __CUDA_ARCH__
+    return __int_as_float(i);
+#else
+    float x; memcpy(&x, &i, 4); return x;
+#endif
+}
+NGP_HD int frexp_exponent(float m) {
+    const int field = (float_bits(m) >> 23) & 0xff;
+    if (field != 0 && field != 0xff) return field - 126;
+    int e; frexpf(m, &e); return e;
+}
+NGP_HD float pow2i(int e) { return bits_float((e + 127) << 23); }   // 2^e, -126 <= e <= 127
+
 NGP_HD uint32_t mip_from_pos(V3 p, uint32_t max_cascade) {
-    int e;
     float m = fmaxf(fmaxf(fabsf(p.x - 0.5f), fabsf(p.y - 0.5f)), fabsf(p.z - 0.5f));
-    frexpf(m, &e);
-    return (uint32_t)clampi(e + 1, 0, (int)max_cascade);
+    return (uint32_t)clampi(frexp_exponent(m) + 1, 0, (int)max_cascade);
 }
 NGP_HD uint32_t mip_from_dt(float dt, V3 p, uint32_t max_cascade) {
     uint32_t mip = mip_from_pos(p, max_cascade);
     dt *= 2 * NERF_GRIDSIZE;
     if (dt < 1.0f) return mip;
-    int e;
-    frexpf(dt, &e);
+    const int e = frexp_exponent(dt);
     // tcnn::clamp(val, lower, upper) = val < lower ? lower : (upper < val ? upper : val)   (testbed_nerf.cu:632)
     int v = (int)mip; const int lo = e, hi = (int)max_cascade;
     v = v < lo ? lo : (hi < v ? hi : v);
     return (uint32_t)v;
 }
 NGP_HD uint32_t cascaded_grid_idx_at(V3 p, uint32_t mip) {
-    float s = scalbnf(1.0f, -(int)mip);
+    float s = pow2i(-(int)mip);   // scalbnf(1.0f, -mip), mip <= 7
     p = (p - v3(0.5f, 0.5f, 0.5f)) * s + v3(0.5f, 0.5f, 0.5f);
     int ix = (int)(p.x * (float)NERF_GRIDSIZE), iy = (int)(p.y * (float)NERF_GRIDSIZE), iz = (int)(p.z * (float)NERF_GRIDSIZE);
     if (ix < 0 || ix >= (int)NERF_GRIDSIZE || iy < 0 || iy >= (int)NERF_GRIDSIZE || iz < 0 || iz >= (int)NERF_GRIDSIZE) return 0xFFFFFFFFu;
@@ -138,8 +159,13 @@ NGP_HD float advance_to_next_voxel(float t, float cone, V3 pos, V3 dir, V3 idir,
 }
 
 NGP_HD float advance_to_next_voxel(float t, const Cone& cone, V3 pos, V3 dir, V3 idir, uint32_t mip) {
-    float res = scalbnf((float)NERF_GRIDSIZE, -(int)mip);
-    float t_target = t + distance_to_next_voxel(pos, dir, idir, res);
+    // res = scalbnf(128, -mip) is a power of two: the division by it in distance_to_next_voxel is the exact multiplication by 2^(mip-7)
+    const float res = pow2i(7 - (int)mip), inv_res = pow2i((int)mip - 7);
+    V3 p = res * (pos - v3(0.5f, 0.5f, 0.5f));
+    float tx = (floorf(p.x + 0.5f + 0.5f * copysignf(1.0f, dir.x)) - p.x) * idir.x;
+    float ty = (floorf(p.y + 0.5f + 0.5f * copysignf(1.0f, dir.y)) - p.y) * idir.y;
+    float tz = (floorf(p.z + 0.5f + 0.5f * copysignf(1.0f, dir.z)) - p.z) * idir.z;
+    float t_target = t + fmaxf(fminf(fminf(tx, ty), tz) * inv_res, 0.0f);
     t = to_stepping_space(t, cone);
     t_target = to_stepping_space(t_target, cone);
     return from_stepping_space(t + ceilf(fmaxf(t_target - t, 0.5f)), cone);
