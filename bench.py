@@ -267,6 +267,8 @@ def run_own(args):
         torch.cuda.profiler.stop()
     clk.__exit__()                              # (NVML polling during the upload pass was measured to slow the H2D copies: stop it first)
     clocks = clk.summary([(t0, t1)])
+    time.sleep(0.25)                            # let the stopped NVML poller go away
+    timed(max(args.warmup, 3), upload=True)     # untimed warm-up of the upload path (copy stream, events, first pinned-page touches)
     ms_e2e, n_e2e, _, _ = timed(args.steps, upload=True)
     view_bytes = int(views[0]["pixels"].numel())
     loss_steps = sum(1 for i in range(args.steps) if i % 16 == 0)
