@@ -249,8 +249,8 @@ void Testbed::train_end(cudaStream_t s, uint32_t measured_override, uint32_t mea
     m_trainer->optimizer_step(s, LOSS_SCALE);   // testbed_nerf.cu:3678 / testbed_image.cu:283
     ++m_training_step;
     if (m_mode == MODE_TB_IMAGE || m_mode == MODE_TB_SDF) {
-        if (m_get_loss) { NGP_CUDA_CHECK(cudaMemcpyAsync(&m_loss_scalar, m_loss_sum.as<float>(), 4, cudaMemcpyDeviceToHost, s)); }
-        NGP_CUDA_CHECK(cudaStreamSynchronize(s));
+        // the host waits only for the loss read-back (every 16th step, testbed.cu:4349-4353); otherwise it runs ahead of the device
+        if (m_get_loss) { NGP_CUDA_CHECK(cudaMemcpyAsync(&m_loss_scalar, m_loss_sum.as<float>(), 4, cudaMemcpyDeviceToHost, s)); NGP_CUDA_CHECK(cudaStreamSynchronize(s)); }
         return;
     }
     // NerfCounters::update_after_training (testbed_nerf.cu:3583-3609): two counters (+ the loss every 16 steps) read back.
