@@ -166,6 +166,15 @@ int ngp_testbed_load_nerf_dataset(ngp_testbed_t t, void* stream, ngp_nerf_datase
  * next training step's loss kernel; RGBA8 views travel on an internal copy stream so that the upload runs beside the start of
  * that step.  The host buffer must stay valid until the next ngp_testbed_train* call has returned. */
 int ngp_testbed_set_training_image(ngp_testbed_t t, void* stream, uint32_t frame_idx, const void* host_pixels);
+/* nerf.training.set_camera_intrinsics(frame_idx, fx, fy, cx, cy, k1, k2, p1, p2) / set_camera_extrinsics(frame_idx, camera_to_world,
+ * convert_to_ngp) (python_api.cu:583-605, testbed_nerf.cu:2873-2919): cx, cy in pixels when >= 0, a normalised principal point
+ * when negative; all-zero distortion = Perspective; camera_to_world = mat4x3 column major, NeRF convention when convert_to_ngp.
+ * An out-of-range frame index is ignored, as in the reference. */
+int ngp_testbed_set_camera_intrinsics(ngp_testbed_t t, void* stream, int32_t frame_idx, float fx, float fy, float cx, float cy,
+                                      float k1, float k2, float p1, float p2);
+int ngp_testbed_set_camera_extrinsics(ngp_testbed_t t, void* stream, int32_t frame_idx, const float* camera_to_world, int32_t convert_to_ngp);
+/* Testbed.reset(reset_density_grid) (python_api.cu: reset_network): fresh parameters, optimizer state and counters */
+int ngp_testbed_reset(ngp_testbed_t t, int32_t reset_density_grid);
 int ngp_testbed_set_image(ngp_testbed_t t, void* stream, const float* host_rgba, int32_t width, int32_t height);   /* image mode */
 /* Sdf mode, Testbed::override_sdf_training_data (python_api.cu:69-99,437): n HOST (point xyz, signed distance) pairs in mesh
  * space; raw_aabb_min/max and mesh_scale are what load_mesh derives from the mesh (m_raw_aabb, m_sdf.mesh_scale) and move the

@@ -97,6 +97,9 @@ SYMBOLS = {
     "ngp_nerf_dataset_view": (i32, [vp, u32, C.POINTER(TrainingImage)]),
     "ngp_testbed_load_nerf_dataset": (i32, [vp, vp, vp]),
     "ngp_testbed_set_training_image": (i32, [vp, vp, u32, vp]),
+    "ngp_testbed_set_camera_intrinsics": (i32, [vp, vp, C.c_int32, f32, f32, f32, f32, f32, f32, f32, f32]),
+    "ngp_testbed_set_camera_extrinsics": (i32, [vp, vp, C.c_int32, vp, C.c_int32]),
+    "ngp_testbed_reset": (i32, [vp, C.c_int32]),
     "ngp_testbed_set_image": (i32, [vp, vp, vp, C.c_int32, C.c_int32]),
     "ngp_testbed_override_sdf_training_data": (i32, [vp, vp, vp, vp, u32, vp, vp, f32]),
     "ngp_testbed_train": (i32, [vp, vp, u32]),

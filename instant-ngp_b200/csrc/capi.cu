@@ -241,11 +241,28 @@ int ngp_testbed_load_nerf_dataset(ngp_testbed_t t, void* stream, ngp_nerf_datase
     for (size_t i = 0; i < views.size(); ++i) fill_view(d->ds.frames[i], &views[i]);
     static_assert(sizeof(ngp_training_image) == sizeof(HostImage), "ABI struct drift");
     t->tb.set_nerf_dataset(S(stream), (uint32_t)views.size(), reinterpret_cast<const HostImage*>(views.data()), d->ds.aabb_scale);
+    t->tb.set_dataset_scale_offset(d->ds.scale, d->ds.offset);
     NGP_API_END
 }
 int ngp_testbed_set_training_image(ngp_testbed_t t, void* stream, uint32_t frame_idx, const void* pixels_host) {
     NGP_API_BEGIN require_device(); NGP_CHECK(t, "null argument");
     t->tb.set_training_image(S(stream), frame_idx, pixels_host);
+    NGP_API_END
+}
+int ngp_testbed_set_camera_intrinsics(ngp_testbed_t t, void* stream, int32_t frame_idx, float fx, float fy, float cx, float cy,
+                                      float k1, float k2, float p1, float p2) {
+    NGP_API_BEGIN require_device(); NGP_CHECK(t, "null argument");
+    t->tb.set_camera_intrinsics(S(stream), frame_idx, fx, fy, cx, cy, k1, k2, p1, p2);
+    NGP_API_END
+}
+int ngp_testbed_set_camera_extrinsics(ngp_testbed_t t, void* stream, int32_t frame_idx, const float* c2w, int32_t convert_to_ngp) {
+    NGP_API_BEGIN require_device(); NGP_CHECK(t && c2w, "null argument");
+    t->tb.set_camera_extrinsics(S(stream), frame_idx, c2w, convert_to_ngp != 0);
+    NGP_API_END
+}
+int ngp_testbed_reset(ngp_testbed_t t, int32_t reset_density_grid) {
+    NGP_API_BEGIN require_device(); NGP_CHECK(t, "null argument");
+    t->tb.reset(reset_density_grid != 0);
     NGP_API_END
 }
 int ngp_testbed_set_image(ngp_testbed_t t, void* stream, const float* rgba, int32_t w, int32_t h) {

@@ -47,7 +47,7 @@ void Testbed::reload_network_from_json(const std::string& json) {
 }
 
 // reset_network (testbed.cu:3903-4151): seeds, counters, network + trainer construction, parameter init
-void Testbed::reset_network() {
+void Testbed::reset_network(bool clear_density_grid) {
     m_rng = Pcg32(seed);                       // testbed.cu:3906
     m_density_grid_rng = Pcg32(m_rng.next_uint());   // testbed.cu:3919 (density_grid_rng seeded from m_rng)
     m_training_step = 0; m_loss_scalar = 0.f;
@@ -59,7 +59,7 @@ void Testbed::reset_network() {
         m_nerf_net = std::make_unique<NerfNetwork>(m_config);
         m_trainer = std::make_unique<Trainer>(m_nerf_net->n_params, m_nerf_net->n_matrix_params, opt);
         m_nerf_net->initialize_params(seed, m_trainer->master, 0);
-        if (m_grid_allocated) {
+        if (m_grid_allocated && clear_density_grid) {
             NGP_CUDA_CHECK(cudaMemset(m_density_grid.ptr, 0, m_density_grid.bytes));
             NGP_CUDA_CHECK(cudaMemset(m_bitfield.ptr, 0, m_bitfield.bytes));
         }
@@ -131,6 +131,47 @@ void Testbed::load_nerf_post(cudaStream_t s, int aabb_scale) {
     m_grid_allocated = true;
     m_training_step = 0; m_density_grid_ema_step = 0;
     NGP_CUDA_CHECK(cudaStreamSynchronize(s));
+}
+
+void Testbed::reset(bool reset_density_grid) {
+    NGP_CHECK(m_have_config, "reset: no network config loaded");
+    NGP_CUDA_CHECK(cudaDeviceSynchronize());
+    m_prefetch_valid = false;
+    reset_network(reset_density_grid);
+}
+
+void Testbed::upload_view_metadata(cudaStream_t s, uint32_t frame_idx) {   // NerfDataset::update_metadata(first, last)
+    if (m_aux_stream) NGP_CUDA_CHECK(cudaStreamSynchronize(m_aux_stream));   // a ray prefetch in flight reads the old metadata
+    m_prefetch_valid = false; ++m_dataset_version;
+    NGP_CUDA_CHECK(cudaMemcpyAsync(m_metas.as<ImageMeta>() + frame_idx, &m_host_metas[frame_idx], sizeof(ImageMeta), cudaMemcpyHostToDevice, s));
+    NGP_CUDA_CHECK(cudaStreamSynchronize(s));
+}
+
+void Testbed::set_camera_intrinsics(cudaStream_t s, int frame_idx, float fx, float fy, float cx, float cy, float k1, float k2, float p1, float p2) {
+    NGP_CHECK(m_mode == MODE_TB_NERF, "set_camera_intrinsics: testbed is not in Nerf mode");
+    if (frame_idx < 0 || frame_idx >= (int)m_n_images) return;   // testbed_nerf.cu:2874-2876
+    if (fx <= 0.f) fx = fy;
+    if (fy <= 0.f) fy = fx;
+    ImageMeta& m = m_host_metas[frame_idx];
+    cx = cx < 0.f ? -cx : cx / (float)m.res[0];
+    cy = cy < 0.f ? -cy : cy / (float)m.res[1];
+    m.lens_mode = LENS_PERSPECTIVE; m.lens_params[0] = m.lens_params[1] = m.lens_params[2] = m.lens_params[3] = 0.f;
+    if (k1 != 0.f || k2 != 0.f || p1 != 0.f || p2 != 0.f) { m.lens_mode = LENS_OPENCV; m.lens_params[0] = k1; m.lens_params[1] = k2; m.lens_params[2] = p1; m.lens_params[3] = p2; }
+    m.principal_point[0] = cx; m.principal_point[1] = cy; m.focal_length[0] = fx; m.focal_length[1] = fy;
+    upload_view_metadata(s, (uint32_t)frame_idx);
+}
+
+void Testbed::set_camera_extrinsics(cudaStream_t s, int frame_idx, const float* c2w, bool convert_to_ngp) {
+    NGP_CHECK(m_mode == MODE_TB_NERF && c2w, "set_camera_extrinsics: testbed is not in Nerf mode / null matrix");
+    if (frame_idx < 0 || frame_idx >= (int)m_n_images) return;   // testbed_nerf.cu:2897-2899
+    float m[12]; memcpy(m, c2w, sizeof(m));
+    if (convert_to_ngp) {   // nerf_matrix_to_ngp (nerf_loader.h:120-140)
+        for (int r = 0; r < 3; ++r) { m[3 + r] *= -1.f; m[6 + r] *= -1.f; m[9 + r] = m[9 + r] * m_ds_scale + m_ds_offset[r]; }
+        float t[12]; memcpy(t, m, sizeof(t));
+        for (int c = 0; c < 4; ++c) { m[c * 3 + 0] = t[c * 3 + 1]; m[c * 3 + 1] = t[c * 3 + 2]; m[c * 3 + 2] = t[c * 3 + 0]; }
+    }
+    memcpy(m_host_metas[frame_idx].xform, m, sizeof(m));
+    upload_view_metadata(s, (uint32_t)frame_idx);
 }
 
 void Testbed::set_training_image(cudaStream_t s, uint32_t frame_idx, const void* pixels_host) {

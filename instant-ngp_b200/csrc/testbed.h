@@ -37,6 +37,15 @@ public:
     // cube with the mesh's raw bounding box and scale; from then on train() runs train_sdf on them (testbed_sdf.cu:1289-1311)
     void override_sdf_training_data(cudaStream_t s, const float* points, const float* distances, uint32_t n, const float* raw_aabb_min,
                                     const float* raw_aabb_max, float mesh_scale);
+    // nerf.training.set_camera_intrinsics / set_camera_extrinsics (testbed_nerf.cu:2873-2919): one view's metadata, host + device copy.
+    // cx, cy: pixels when >= 0, already-normalised principal point when negative; k1 k2 p1 p2 all zero = Perspective.
+    // convert_to_ngp: `camera_to_world` is a NeRF-convention mat4x3 (column major) and goes through nerf_matrix_to_ngp with the
+    // scale / offset the data set was loaded with (0.33 / 0.5 for views handed over in memory)
+    void set_camera_intrinsics(cudaStream_t s, int frame_idx, float fx, float fy, float cx, float cy, float k1, float k2, float p1, float p2);
+    void set_camera_extrinsics(cudaStream_t s, int frame_idx, const float* camera_to_world, bool convert_to_ngp);
+    void set_dataset_scale_offset(float scale, const float* offset3) { m_ds_scale = scale; for (int k = 0; k < 3; ++k) m_ds_offset[k] = offset3[k]; }
+    // Testbed::reset_network(clear_density_grid) (python_api.cu "reset"): fresh parameters, optimizer state, counters
+    void reset(bool reset_density_grid);
     // nerf.training.set_image (python_api.cu:49-67): replace the pixels of one training view (same resolution / type),
     // host -> device; asynchronous with respect to the host when the source is pinned.  RGBA8 views are copied on an internal
     // copy stream, ordered after everything already queued on `s` and before the next training step's loss kernel, so the
@@ -93,7 +102,8 @@ public:
     const std::vector<ImageMeta>& training_views() const { return m_host_metas; }
 
 private:
-    void reset_network();
+    void reset_network(bool clear_density_grid = true);
+    void upload_view_metadata(cudaStream_t s, uint32_t frame_idx);
     void load_nerf_post(cudaStream_t s, int aabb_scale);                                           // testbed_nerf.cu:3046-3112
     void training_prep_nerf(cudaStream_t s);                                                       // testbed_nerf.cu:4137-4152
     void update_density_grid_nerf(cudaStream_t s, float decay, uint32_t n_uniform, uint32_t n_nonuniform);   // :3412-3536
@@ -127,6 +137,7 @@ private:
     std::vector<void*> m_image_buffers; std::vector<size_t> m_image_bytes; DeviceBuffer m_metas; std::vector<ImageMeta> m_host_metas;
     DeviceBuffer m_density_grid, m_density_grid_tmp, m_bitfield, m_mean, m_partials, m_grid_pos, m_grid_idx, m_grid_out;
     uint32_t m_density_grid_ema_step = 0; bool m_grid_allocated = false;
+    float m_ds_scale = 0.33f, m_ds_offset[3] = {0.5f, 0.5f, 0.5f};   // NerfDataset::scale / offset (nerf_loader.h:29, nerf_loader.cu:392-393)
     // NerfCounters (testbed.h:433-447)
     uint32_t m_rays_per_batch = 1u << 12, m_n_rays_total = 0, m_measured = 0, m_measured_before = 0;
     // per-step scratch

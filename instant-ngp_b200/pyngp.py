@@ -170,6 +170,21 @@ class Testbed:
             pixels = np.ascontiguousarray(pixels); ptr = pixels.ctypes.data
         check(lib().ngp_testbed_set_training_image(self._h, _stream(), int(frame_idx), C.c_void_p(ptr)))
 
+    def set_camera_intrinsics(self, frame_idx, fx=0.0, fy=0.0, cx=-0.5, cy=-0.5, k1=0.0, k2=0.0, p1=0.0, p2=0.0):
+        """nerf.training.set_camera_intrinsics (python_api.cu:583-593)"""
+        check(lib().ngp_testbed_set_camera_intrinsics(self._h, _stream(), int(frame_idx), fx, fy, cx, cy, k1, k2, p1, p2))
+
+    def set_camera_extrinsics(self, frame_idx, camera_to_world, convert_to_ngp=True):
+        """nerf.training.set_camera_extrinsics (python_api.cu:594-605); camera_to_world: 3x4 (rows) or 4x4 row-major matrix"""
+        m = np.asarray(camera_to_world, np.float32)
+        if m.shape not in ((3, 4), (4, 4)):
+            raise RuntimeError("camera_to_world must be a 3x4 or 4x4 matrix")
+        col_major = np.ascontiguousarray(m[:3, :4].T).reshape(-1)
+        check(lib().ngp_testbed_set_camera_extrinsics(self._h, _stream(), int(frame_idx), col_major.ctypes.data_as(C.c_void_p), int(convert_to_ngp)))
+
+    def reset(self, reset_density_grid=True):
+        check(lib().ngp_testbed_reset(self._h, int(reset_density_grid)))
+
     def set_image(self, rgba):
         rgba = np.ascontiguousarray(rgba, np.float32)
         assert rgba.ndim == 3 and rgba.shape[2] == 4

@@ -282,3 +282,39 @@ def test_render_matches_oracle_and_tiles(env, ref):
     rgba, depth = ref.render_nerf(rc, ref.nerf_cfg_from_json(SMALL_CFG), params, bf)
     assert np.abs(full - rgba).max() <= 2e-2, np.abs(full - rgba).max()
     assert np.abs(full - rgba).mean() <= 1e-3
+
+
+def test_camera_setters_and_reset(env):
+    """nerf.training.set_camera_intrinsics / set_camera_extrinsics (testbed_nerf.cu:2873-2919) and Testbed.reset"""
+    tb, ref_tb = _testbed(env), _testbed(env)
+    v0 = tb.training_view(2)
+    x = np.asarray(v0["xform"], np.float64).reshape(4, 3).T            # NGP 3x4
+    nerf = x[[2, 0, 1], :].copy(); nerf[:, 1] *= -1; nerf[:, 2] *= -1; nerf[:, 3] = (nerf[:, 3] - 0.5) / 0.33      # ngp_matrix_to_nerf
+    tb.set_camera_extrinsics(2, np.eye(4)[:3], convert_to_ngp=False)
+    assert np.array_equal(tb.training_view(2)["xform"], np.eye(4, dtype=np.float32)[:3, :4].T.reshape(-1))
+    tb.set_camera_extrinsics(2, nerf, convert_to_ngp=True)
+    np.testing.assert_allclose(tb.training_view(2)["xform"], v0["xform"], atol=1e-6)
+    tb.set_camera_extrinsics(2, x, convert_to_ngp=False)                # exact restore
+    assert np.array_equal(tb.training_view(2)["xform"], v0["xform"])
+    tb.set_camera_intrinsics(2, fx=100.0, cx=24.0, cy=-0.25, k1=0.1, p2=0.01)
+    v = tb.training_view(2)
+    assert v["focal_length"] == (100.0, 100.0) and v["principal_point"] == (24.0 / RES, 0.25) and v["lens_mode"] == 1
+    assert v["lens_params"] == (np.float32(0.1), 0.0, 0.0, np.float32(0.01))
+    tb.set_camera_intrinsics(2, fx=v0["focal_length"][0], fy=v0["focal_length"][1], cx=-0.5, cy=-0.5)
+    v = tb.training_view(2)
+    assert v["lens_mode"] == 0 and v["focal_length"] == v0["focal_length"] and v["principal_point"] == (0.5, 0.5)
+    tb.set_camera_intrinsics(N_VIEWS + 5, fx=1.0)                       # out of range: ignored
+    # the device copy is what the sampler reads: with everything restored the first step is identical to an untouched testbed's
+    tb.train(BATCH); ref_tb.train(BATCH)
+    n = ref_tb.stats.rays_per_batch
+    assert torch.equal(tb.debug_tensor("rays", torch.float32, n * 6), ref_tb.debug_tensor("rays", torch.float32, n * 6))
+    assert torch.equal(tb.param_buffer(0), ref_tb.param_buffer(0))
+    # reset: step counter, counters and parameters as after reload_network
+    fresh = _testbed(env)
+    for _ in range(5):
+        tb.train(BATCH)
+    tb.reset()
+    assert tb.training_step == 0 and tb.stats.rays_per_batch == 4096
+    assert torch.equal(tb.param_buffer(0), fresh.param_buffer(0)) and float(tb.density_grid(0).abs().sum()) == 0.0
+    tb.train(BATCH); fresh.train(BATCH)
+    assert torch.equal(tb.param_buffer(0), fresh.param_buffer(0))
