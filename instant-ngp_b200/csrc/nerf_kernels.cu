@@ -1331,12 +1331,14 @@ __global__ void shade_kernel(uint32_t n_hit, RaysSoa hit, bool linear_colors, ui
 
 void nerf_init_rays(cudaStream_t s, const RenderCamera& cam, uint32_t sample_index, bool snap, Aabb render_aabb, const uint8_t* bitfield,
                     uint32_t max_mip, float cone, RaysSoa rays, float* frame_rgba, float* frame_depth) {
+    NGP_PROFILE_SCOPE(s, "render_init_rays", (uint64_t)cam.res[0] * (uint64_t)(cam.y1 - cam.y0));
     const dim3 threads = {16, 8, 1};
     const dim3 blocks = {div_round_up((uint32_t)cam.res[0], 16), div_round_up((uint32_t)(cam.y1 - cam.y0), 8), 1};
     init_rays_kernel<<<blocks, threads, 0, s>>>(cam, sample_index, snap, render_aabb, bitfield, max_mip, cone, rays, frame_rgba, frame_depth);
     NGP_POST_LAUNCH();
 }
 void nerf_compact_rays(cudaStream_t s, uint32_t n, RaysSoa src, RaysSoa dst, RaysSoa hit, uint32_t* counters, uint32_t* scan_scratch) {
+    NGP_PROFILE_SCOPE(s, "render_compact", n);
     const uint32_t blocks = div_round_up(n, SCAN_BLOCK);
     compact_count_kernel<<<blocks, SCAN_BLOCK, 0, s>>>(n, src.payload, scan_scratch); NGP_POST_LAUNCH();
     scan_block_totals_kernel<<<1, 1024, 0, s>>>(blocks, scan_scratch, nullptr, &counters[0], nullptr, false); NGP_POST_LAUNCH();
@@ -1344,11 +1346,13 @@ void nerf_compact_rays(cudaStream_t s, uint32_t n, RaysSoa src, RaysSoa dst, Ray
 }
 void nerf_generate_next_inputs(cudaStream_t s, uint32_t n_alive, Aabb render_aabb, Aabb train_aabb, RaysSoa rays, float* input, uint32_t n_steps,
                                const uint8_t* bitfield, uint32_t max_mip, float cone) {
+    NGP_PROFILE_SCOPE(s, "render_next_inputs", n_alive);
     next_inputs_kernel<<<div_round_up(n_alive, 128), 128, 0, s>>>(n_alive, render_aabb, train_aabb, rays, input, n_steps, bitfield, max_mip, cone);
     NGP_POST_LAUNCH();
 }
 void nerf_composite(cudaStream_t s, uint32_t n_alive, uint32_t current_step, Aabb train_aabb, const float* camera, RaysSoa rays, const float* input,
                     const __half* output, uint32_t n_steps, int rgb_act, int density_act, float min_transmittance) {
+    NGP_PROFILE_SCOPE(s, "render_composite", n_alive);
     composite_kernel<<<div_round_up(n_alive, 128), 128, 0, s>>>(n_alive, current_step, train_aabb, nullptr, camera[6], camera[7], camera[8], camera[9], camera[10],
                                                                 camera[11], rays, input, output, n_steps, rgb_act, density_act, min_transmittance);
     NGP_POST_LAUNCH();
