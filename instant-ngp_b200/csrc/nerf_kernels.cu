@@ -276,14 +276,7 @@ NGP_D void random_image_pos_training(Pcg32& rng, const int* res, bool snap, floa
 // the mip is always 0, the voxel resolution is the constant 128 and to/from_stepping_space are t / S and n * S, so the
 // generic helpers collapse to the expressions below — the same float operations in the same order (the division by the
 // power-of-two resolution is written as the exact multiplication by its inverse), hence the same bits.
-// t / MIN_CONE_STEPSIZE() without the generic IEEE-division sequence: q = t * (1/S) refined by one exact-residual FMA step
-// is the correctly rounded quotient; verified EXHAUSTIVELY against t / S for every float in [1e-30, 2048)
-// (tools/verify_fast_div.c: 1 157 627 904 values, 0 mismatches); outside that range the plain division is used.
-NGP_D float div_by_stepsize(float t) {
-    constexpr float S = SQRT3 / (float)NERF_STEPS, RS = 1.0f / S;
-    if (t >= 1e-30f && t < 2048.0f) { const float q = t * RS; return fmaf(fmaf(-q, S, t), RS, q); }
-    return t / S;
-}
+// (div_by_stepsize: nerf_device.cuh)
 // where the counting walk leaves (t, dt) of the samples it finds: a fixed window per ray plus, for the few rays that
 // outgrow it, a whole-ray slot (NERF_STEPS entries) taken from a pool with one atomicAdd
 struct SampleLog {
