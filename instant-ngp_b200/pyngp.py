@@ -387,6 +387,31 @@ class Testbed:
             return torch.cat([rgb, px[..., 3:4]], dim=2)
         return _wrap(v["device_pixels"], w * h * 4, torch.float32).view(h, w, 4).clone()
 
+    def evaluate_training_views(self, view_indices=None, spp=8):
+        """The evaluation protocol of scripts/run.py:208-266, headless: black background, rays through pixel centres,
+        render_min_transmittance 1e-4, spp samples per pixel, each view rendered at its own resolution with its own lens and
+        compared with its ground-truth pixels in sRGB after clipping.  Returns {"psnr", "min_psnr", "max_psnr", "mse", "n"}
+        (psnr = mean of the per-view values, as run.py reports it)."""
+        idx = list(range(self.n_training_views())) if view_indices is None else list(view_indices)
+        saved = (self.snap_to_pixel_centers, self.render_min_transmittance)
+        self.background_color = [0.0, 0.0, 0.0]
+        self.snap_to_pixel_centers = True
+        self.render_min_transmittance = 1e-4
+
+        def to_srgb(x):
+            return np.where(x < 0.0031308, 12.92 * x, 1.055 * np.power(np.maximum(x, 1e-12), 0.41666) - 0.055)   # common.py linear_to_srgb
+        psnrs, mses = [], []
+        try:
+            for i in idx:
+                img = self.render_training_view(i, spp)
+                ref = self.training_view_pixels(i).cpu().numpy()
+                a = np.clip(to_srgb(img[..., :3]), 0.0, 1.0); r = np.clip(to_srgb(ref[..., :3]), 0.0, 1.0)
+                mse = float(((a - r) ** 2).mean())
+                mses.append(mse); psnrs.append(-10.0 * np.log10(max(mse, 1e-12)))
+        finally:
+            self.snap_to_pixel_centers, self.render_min_transmittance = saved
+        return {"psnr": float(np.mean(psnrs)), "min_psnr": float(np.min(psnrs)), "max_psnr": float(np.max(psnrs)), "mse": float(np.mean(mses)), "n": len(idx)}
+
     def compute_image_mse(self, quantize=False):
         v = C.c_float()
         check(lib().ngp_testbed_compute_image_mse(self._h, _stream(), int(quantize), C.byref(v)))

@@ -258,6 +258,10 @@ def test_training_converges_and_renders(env):
     assert losses[-1] < 0.5 * losses[0], losses
     assert p1 > p0 + 5 and p1 > 20, (p0, p1)
     assert np.isfinite(img).all() and img[..., 3].max() > 0.9
+    # the run.py evaluation protocol (sRGB, black background, view's own camera): same scene, same ballpark as the linear PSNR above
+    ev = tb.evaluate_training_views([0, 5], spp=2)
+    assert ev["n"] == 2 and ev["min_psnr"] <= ev["psnr"] <= ev["max_psnr"] and ev["max_psnr"] > 20 and ev["psnr"] > 15, ev   # 300 small steps: floaters weigh more in sRGB
+    assert tb.render_min_transmittance == pytest.approx(0.01) and tb.snap_to_pixel_centers     # knobs restored
 
 
 def test_render_matches_oracle_and_tiles(env, ref):

@@ -33,22 +33,8 @@ CONFIGS = {
 }
 
 
-def linear_to_srgb(x):
-    return np.where(x < 0.0031308, 12.92 * x, 1.055 * np.power(np.maximum(x, 1e-12), 0.41666) - 0.055)
-
-
 def psnr_on_training_views(tb, views, spp):
-    tb.background_color = [0.0, 0.0, 0.0]
-    tb.snap_to_pixel_centers = True
-    tb.render_min_transmittance = 1e-4
-    tot = 0.0
-    for i in views:
-        img = tb.render_training_view(i, spp)
-        ref = tb.training_view_pixels(i).cpu().numpy()
-        a = np.clip(linear_to_srgb(img[..., :3]), 0, 1); r = np.clip(linear_to_srgb(ref[..., :3]), 0, 1)
-        tot += -10 * np.log10(max(float(((a - r) ** 2).mean()), 1e-12))
-    tb.render_min_transmittance = 0.01
-    return tot / len(views)
+    return tb.evaluate_training_views(views, spp)["psnr"]      # scripts/run.py:208-266 protocol, see pyngp.Testbed.evaluate_training_views
 
 
 def main():
