@@ -52,8 +52,9 @@ class Encoding:
         self.n_dims = n_dims_to_encode
 
     def __del__(self):
-        if getattr(self, "_h", None):
+        if getattr(self, "_h", None) and lib is not None:     # `lib` is already torn down when the interpreter exits
             lib().ngp_encoding_destroy(self._h)
+            self._h = None
 
     def n_params(self):
         return lib().ngp_encoding_n_params(self._h)
@@ -108,8 +109,9 @@ class NerfNetwork:
         self.off_density, self.off_rgb, self.off_encoding, self.n_matrix_params = a.value, b.value, c.value, d.value
 
     def __del__(self):
-        if getattr(self, "_h", None):
+        if getattr(self, "_h", None) and lib is not None:     # `lib` is already torn down when the interpreter exits
             lib().ngp_nerf_network_destroy(self._h)
+            self._h = None
 
     def n_params(self):
         return lib().ngp_nerf_network_n_params(self._h)
@@ -150,8 +152,9 @@ class NetworkWithInputEncoding:
         self.off_mlp, self.off_encoding, self.n_matrix_params = a.value, b.value, c.value
 
     def __del__(self):
-        if getattr(self, "_h", None):
+        if getattr(self, "_h", None) and lib is not None:     # `lib` is already torn down when the interpreter exits
             lib().ngp_encoded_mlp_destroy(self._h)
+            self._h = None
 
     def n_params(self):
         return lib().ngp_encoded_mlp_n_params(self._h)

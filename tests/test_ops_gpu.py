@@ -96,9 +96,13 @@ def test_grid_backward_scatter(ops, ref, case):
     g = enc.backward(_cuda(x), _cuda(dy)).float().cpu().numpy().astype(np.float64)
     gr = ref.grid_backward(cfg, x, dy, enc.n_params())
     gabs = ref.grid_backward(cfg, x, np.abs(dy), enc.n_params())     # sum |contrib| bound
-    tol = 2.0 ** -9 * gabs + 1e-6                                    # fp16 atomics: one rounding per accumulated term
+    # fp16 atomics: one rounding per accumulated term, in an order that changes from run to run.  Measured over 40 repetitions per case
+    # (tools/backward_tolerance_stats.py): the worst entry reaches 1.45 x (2^-9 * sum|contrib|), and up to 6 entries of the small,
+    # heavily accumulated tables exceed 2^-9 in a run -> a handful of entries may pass 2^-9, none may pass 2^-8
+    tol = 2.0 ** -9 * gabs + 1e-6
     bad = np.abs(g - gr) > tol
-    assert bad.mean() < 1e-4, (bad.sum(), np.abs(g - gr).max())
+    assert bad.sum() <= max(16, 1e-4 * bad.size), (bad.sum(), np.abs(g - gr).max())
+    assert (np.abs(g - gr) <= 2 * tol).all(), (np.abs(g - gr) / tol).max()
     # conservation: sum of all gradients of a level == sum of dy of that level (weights sum to 1)
     _, off, _, _ = ref.grid_layout(cfg)
     for l in range(L):
