@@ -58,8 +58,64 @@ _FLOAT_OPTS = {"near_distance", "density_grid_decay", "render_min_transmittance"
 _INT_OPTS = {"loss_type", "rgb_activation", "density_activation", "seed", "sampler_lanes_per_ray", "prefetch_hits"}
 
 
+class RandomMode(enum.IntEnum):       # python_api.cu:299-305
+    Random = 0
+    Halton = 1
+    Sobol = 2
+    Stratified = 3
+
+
+class _Namespace:
+    """One level of the reference binding's attribute tree (`testbed.nerf.training.near_distance`, python_api.cu:550-695): attribute
+    reads and writes are forwarded to the flat option of the owning Testbed named in `fields`; `extra` holds child namespaces and
+    bound methods."""
+    def __init__(self, tb, fields, extra=None):
+        object.__setattr__(self, "_tb", tb)
+        object.__setattr__(self, "_fields", fields)
+        object.__setattr__(self, "_extra", extra or {})
+
+    def __getattr__(self, name):
+        if name in self._extra:
+            v = self._extra[name]
+            return v() if isinstance(v, _Lazy) else v
+        if name in self._fields:
+            return getattr(self._tb, self._fields[name])
+        raise AttributeError(name)
+
+    def __setattr__(self, name, value):
+        if name not in self._fields:
+            raise AttributeError(f"{name} is not a writable member on this path")
+        setattr(self._tb, self._fields[name], value)
+
+
+class _Lazy:
+    def __init__(self, fn):
+        self.fn = fn
+
+    def __call__(self):
+        return self.fn()
+
+
+class _Dataset:
+    """nerf.training.dataset: n_images, aabb_scale-free view of the loaded metadata (nerf_loader.h:110-171)"""
+    def __init__(self, tb):
+        self._tb = tb
+
+    @property
+    def n_images(self):
+        return self._tb.n_training_views()
+
+    @property
+    def metadata(self):
+        class M:
+            def __init__(s, v):
+                s.resolution = list(v["res"]); s.focal_length = list(v["focal_length"]); s.principal_point = list(v["principal_point"])
+        return [M(self._tb.training_view(i)) for i in range(self.n_images)]
+
+
 class Testbed:
-    def __init__(self, mode=TestbedMode.Nerf):
+    def __init__(self, mode=TestbedMode.Nerf, data_path=None, network_config=None):
+        """Testbed(mode) / Testbed(mode, data_path, config_path | json) (python_api.cu:388-390)"""
         object.__setattr__(self, "_h", C.c_void_p())
         check(lib().ngp_testbed_create(int(mode), C.byref(self._h)))
         object.__setattr__(self, "mode", TestbedMode(int(mode)))
@@ -67,6 +123,24 @@ class Testbed:
         object.__setattr__(self, "shall_train", True)
         object.__setattr__(self, "_keep", [])
         object.__setattr__(self, "_dist", None)
+        training = _Namespace(self, {"random_bg_color": "random_bg_color", "loss_type": "loss_type", "near_distance": "near_distance",
+                                     "density_grid_decay": "density_grid_decay", "linear_colors": "linear_colors",
+                                     "snap_to_pixel_centers": "snap_to_pixel_centers"},
+                              {"set_image": self.set_training_image, "set_camera_intrinsics": self.set_camera_intrinsics,
+                               "set_camera_extrinsics": self.set_camera_extrinsics, "dataset": _Dataset(self),
+                               "n_images_for_training": _Lazy(self.n_training_views)})
+        object.__setattr__(self, "nerf", _Namespace(self, {"rgb_activation": "rgb_activation", "density_activation": "density_activation",
+                                                           "cone_angle_constant": "cone_angle_constant",
+                                                           "render_min_transmittance": "render_min_transmittance"}, {"training": training}))
+        image_training = _Namespace(self, {"snap_to_pixel_centers": "image_snap_to_pixel_centers", "linear_colors": "image_linear_colors"})
+        object.__setattr__(self, "image", _Namespace(self, {"random_mode": "image_random_mode"}, {"training": image_training}))
+        if data_path is not None:
+            self.load_training_data(data_path)
+        if network_config is not None:
+            if isinstance(network_config, (dict,)) or (isinstance(network_config, str) and network_config.lstrip().startswith("{")):
+                self.reload_network_from_json(network_config)
+            else:
+                self.reload_network_from_file(network_config)
 
     def __del__(self):
         h = getattr(self, "_h", None)
@@ -79,6 +153,13 @@ class Testbed:
 
     # ---- runtime knobs (def_readwrite members) ----
     def __getattr__(self, name):
+        if name == "background_color":
+            out = []
+            for k in "rgb":
+                v = C.c_double(); check(lib().ngp_testbed_get_option(self._h, f"background_{k}".encode(), C.byref(v))); out.append(v.value)
+            return out
+        if name == "image_random_mode":      # image.random_mode (python_api.cu:686): Stratified <-> image_stratified, everything else plain random
+            return RandomMode.Stratified if self.image_stratified else RandomMode.Random
         if name in _BOOL_OPTS | _FLOAT_OPTS | _INT_OPTS:
             v = C.c_double()
             check(lib().ngp_testbed_get_option(self._h, name.encode(), C.byref(v)))
@@ -88,6 +169,8 @@ class Testbed:
     def __setattr__(self, name, value):
         if name in _BOOL_OPTS | _FLOAT_OPTS | _INT_OPTS:
             check(lib().ngp_testbed_set_option(self._h, name.encode(), float(value)))
+        elif name == "image_random_mode":
+            self.image_stratified = int(value) == int(RandomMode.Stratified)
         elif name == "background_color":
             for k, c in zip("rgb", value):
                 check(lib().ngp_testbed_set_option(self._h, f"background_{k}".encode(), float(c)))

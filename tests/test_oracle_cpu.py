@@ -5,6 +5,7 @@ import os
 import re
 
 import numpy as np
+import pytest
 
 from .conftest import ROOT
 
@@ -241,3 +242,29 @@ def test_tcnn_losses_gradient_is_the_derivative_of_the_value(ref):
     t2 = ref.lib().ref_l2_loss(ref.P(pred), 16, ref.P(target), n, 128.0, ref.P(rdl))
     total, dl = ref.tcnn_loss("L2", pred, target, 3, 128.0)
     assert np.array_equal(dl, rdl) and abs(total - t2) < 1e-9
+
+
+def test_pyngp_attribute_tree_matches_the_reference_binding(ngp):
+    """testbed.nerf.training.* / testbed.nerf.* / testbed.image.* (python_api.cu:550-695) forward to the library's options;
+    host-only (no device needed for option access)."""
+    import importlib
+    pyngp = importlib.import_module("instant-ngp_b200.pyngp")
+    tb = pyngp.Testbed(pyngp.TestbedMode.Nerf)
+    assert tb.nerf.training.random_bg_color is True and tb.nerf.training.near_distance == pytest.approx(0.1)
+    tb.nerf.training.random_bg_color = False
+    tb.nerf.training.near_distance = 0.25
+    tb.nerf.training.loss_type = pyngp.LossType.Huber
+    tb.nerf.render_min_transmittance = 1e-4
+    tb.nerf.rgb_activation = pyngp.NerfActivation.Exponential
+    assert tb.random_bg_color is False and tb.near_distance == pytest.approx(0.25) and tb.loss_type == int(pyngp.LossType.Huber)
+    assert tb.render_min_transmittance == pytest.approx(1e-4) and tb.nerf.rgb_activation == int(pyngp.NerfActivation.Exponential)
+    tb.background_color = [0.1, 0.2, 0.3]
+    assert tb.background_color == pytest.approx([0.1, 0.2, 0.3])
+    assert tb.nerf.training.dataset.n_images == 0 and tb.nerf.training.n_images_for_training == 0
+    with pytest.raises(AttributeError):
+        tb.nerf.training.optimize_extrinsics = True          # default-off feature outside the path: fails loudly rather than silently
+    img = pyngp.Testbed(pyngp.TestbedMode.Image)
+    assert img.image.random_mode == pyngp.RandomMode.Stratified
+    img.image.random_mode = pyngp.RandomMode.Random
+    img.image.training.snap_to_pixel_centers = False
+    assert img.image_stratified is False and img.image_snap_to_pixel_centers is False
