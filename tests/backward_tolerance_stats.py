@@ -1,3 +1,5 @@
+"""Margin of the hash-grid backward tolerance over repeated runs (fp16 atomics in run-dependent order) - a helper of tests/test_ops_gpu.py,
+run by hand on a GPU box: python tests/backward_tolerance_stats.py"""
 import sys, importlib
 sys.path.insert(0, "/root/repo")
 import numpy as np, torch

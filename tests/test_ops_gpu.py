@@ -97,7 +97,7 @@ def test_grid_backward_scatter(ops, ref, case):
     gr = ref.grid_backward(cfg, x, dy, enc.n_params())
     gabs = ref.grid_backward(cfg, x, np.abs(dy), enc.n_params())     # sum |contrib| bound
     # fp16 atomics: one rounding per accumulated term, in an order that changes from run to run.  Measured over 40 repetitions per case
-    # (tools/backward_tolerance_stats.py): the worst entry reaches 1.45 x (2^-9 * sum|contrib|), and up to 6 entries of the small,
+    # (tests/backward_tolerance_stats.py): the worst entry reaches 1.45 x (2^-9 * sum|contrib|), and up to 6 entries of the small,
     # heavily accumulated tables exceed 2^-9 in a run -> a handful of entries may pass 2^-9, none may pass 2^-8
     tol = 2.0 ** -9 * gabs + 1e-6
     bad = np.abs(g - gr) > tol
