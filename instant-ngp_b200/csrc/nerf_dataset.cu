@@ -164,7 +164,7 @@ NerfDataset::NerfDataset(const std::vector<std::string>& json_paths) {
         for (size_t fi = 0; fi < kept[ji].size(); ++fi) {
             const Json& fr = kept[ji][fi];
             DatasetFrame d;
-            d.json_index = ji; d.frame_index = fi;
+            d.json_index = ji; d.frame_index = fi; d.white_transparent = white_transparent; d.black_transparent = black_transparent;
             d.file_path = fr.at("file_path").str;
             d.resolved_path = resolve_path(base, d.file_path);
             const Json& mat = fr.contains("transform_matrix_start") ? fr.at("transform_matrix_start") : fr.at("transform_matrix");
@@ -188,11 +188,11 @@ void NerfDataset::set_image(size_t i, const void* pixels, int data_type, int w, 
     d.res[0] = w; d.res[1] = h; d.data_type = data_type;
     const size_t n = (size_t)w * h, bytes = n * (data_type == IMG_BYTE ? 4 : 16);
     d.pixels.assign((const uint8_t*)pixels, (const uint8_t*)pixels + bytes);
-    if (data_type == IMG_BYTE && (white_transparent || black_transparent)) {   // convert_rgba32 (nerf_loader.cu:49-71)
+    if (data_type == IMG_BYTE && (d.white_transparent || d.black_transparent)) {   // convert_rgba32 (nerf_loader.cu:49-71)
         for (size_t p = 0; p < n; ++p) {
             uint8_t* q = &d.pixels[p * 4];
-            if (white_transparent && q[0] == 255 && q[1] == 255 && q[2] == 255) q[3] = 0;
-            if (black_transparent && q[0] == 0 && q[1] == 0 && q[2] == 0) q[3] = 0;
+            if (d.white_transparent && q[0] == 255 && q[1] == 255 && q[2] == 255) q[3] = 0;
+            if (d.black_transparent && q[0] == 0 && q[1] == 0 && q[2] == 0) q[3] = 0;
         }
     }
     const Json& json = m_jsons[d.json_index];

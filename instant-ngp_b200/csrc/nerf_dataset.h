@@ -22,6 +22,7 @@ struct DatasetFrame {
     int data_type = 0;            // 0 RGBA8, 1 RGBA float32
     std::vector<uint8_t> pixels;  // converted copy (white/black-transparent rules of convert_rgba32, nerf_loader.cu:49-71)
     size_t json_index = 0, frame_index = 0;   // which json / which frame of it (after sorting and culling)
+    bool white_transparent = false, black_transparent = false;   // the scene flags as they stood when this frame's json was read (LoadedImageInfo defaults)
 };
 
 class NerfDataset {

@@ -464,6 +464,8 @@ class Testbed:
         """the device copy of training view i as float32 [H,W,4] linear premultiplied RGBA (what render_ground_truth shows)"""
         v = self.training_view(i)
         w, h = v["res"]
+        if not v["device_pixels"]:
+            raise RuntimeError("training view has no pixels (metadata restored from a snapshot: load the data set to get the images)")
         if v["data_type"] == 0:
             px = _wrap(v["device_pixels"], w * h * 4, torch.uint8).view(h, w, 4).float() / 255.0
             rgb = torch.where(px[..., :3] <= 0.04045, px[..., :3] / 12.92, ((px[..., :3] + 0.055) / 1.055) ** 2.4) * px[..., 3:4]

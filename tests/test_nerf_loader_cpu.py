@@ -140,3 +140,39 @@ def test_fox_scene_of_the_reference_mount(L):
     _compare(cpp, ref)
     assert n_all == 67 and len(cpp["frames"]) == 50 and cpp["aabb_scale"] == 8      # frames whose JPEG is absent are dropped
     assert all(os.path.exists(f["path"]) for f in cpp["frames"])
+
+
+def test_transparency_rules_and_multiple_json_files(L, tmp_path):
+    """convert_rgba32 (nerf_loader.cu:49-71): white / black pixels become transparent when the scene asks for it; several json files
+    describe one scene (load_nerf takes a vector of paths), frames are appended file by file."""
+    rng = np.random.default_rng(4)
+    a = tmp_path / "a"; b = tmp_path / "b"; a.mkdir(); b.mkdir()
+    pa = _write_scene(a, {"fl_x": 50.0, "white_transparent": True, "aabb_scale": 2}, [{"file_path": f"w{i}.png", "transform_matrix": _pose(rng)} for i in range(2)])
+    pb = _write_scene(b, {"fl_x": 60.0, "black_transparent": True}, [{"file_path": f"k{i}.png", "transform_matrix": _pose(rng)} for i in range(3)])
+    lib = L.lib(); d = C.c_void_p()
+    L.check(lib.ngp_nerf_dataset_open(f"{pa}\n{pb}".encode(), C.byref(d)))
+    try:
+        assert lib.ngp_nerf_dataset_n_images(d) == 5
+        px = np.zeros((2, 3, 4), np.uint8); px[..., 3] = 255
+        px[0, 0, :3] = 255; px[0, 1, :3] = (255, 255, 254); px[1, 0, :3] = 0; px[1, 1, :3] = (0, 1, 0)
+        buf = C.create_string_buffer(4096)
+        names = []
+        for i in range(5):
+            L.check(lib.ngp_nerf_dataset_image_path(d, i, buf, 4096)); names.append(os.path.basename(buf.value.decode()))
+            L.check(lib.ngp_nerf_dataset_set_image(d, i, px.ctypes.data_as(C.c_void_p), 0, 3, 2))
+        assert names == ["w0.png", "w1.png", "k0.png", "k1.png", "k2.png"]
+        v = L.TrainingImage()
+        L.check(lib.ngp_nerf_dataset_view(d, 4, C.byref(v)))
+        got = np.ctypeslib.as_array(C.cast(v.pixels, C.POINTER(C.c_uint8)), shape=(2, 3, 4)).copy()
+        # a flag stays set for the files that follow (the reference keeps `info` across the files): the second file's frames obey both
+        assert got[0, 0, 3] == 0 and got[1, 0, 3] == 0                    # pure white, pure black -> transparent
+        assert got[0, 1, 3] == 255 and got[1, 1, 3] == 255                # anything else keeps its alpha
+        assert np.array_equal(got[..., :3], px[..., :3])
+        assert tuple(v.focal_length) == (60.0, 60.0)                      # the second file's intrinsics for its own frames
+        L.check(lib.ngp_nerf_dataset_view(d, 0, C.byref(v)))
+        assert tuple(v.focal_length) == (50.0, 50.0)
+        first = np.ctypeslib.as_array(C.cast(v.pixels, C.POINTER(C.c_uint8)), shape=(2, 3, 4))
+        assert first[0, 0, 3] == 0 and first[1, 0, 3] == 255              # the first file only knows white_transparent
+        a_s = C.c_int32(); L.check(lib.ngp_nerf_dataset_info(d, C.byref(a_s), None, None, None)); assert a_s.value == 2
+    finally:
+        lib.ngp_nerf_dataset_close(d)
