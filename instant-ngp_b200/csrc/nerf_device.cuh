@@ -5,6 +5,7 @@
 // oracle (no implicit FMA contraction, explicit fmaf where fused) so traversal decisions are bit-exact.
 #pragma once
 #include "ngp_common.cuh"
+#include "../../include/ngp_b200_math.h"
 
 namespace ngp {
 
@@ -37,30 +38,9 @@ struct ImageMeta {
     float xform[12];
 };
 
-// ---- stepping (testbed_nerf.cu:124-184) ----
-NGP_HD float to_stepping_space(float t, float cone_angle) {
-    if (cone_angle <= 1e-5f) return t / MIN_CONE_STEPSIZE();
-    float log1p_c = logf(1.0f + cone_angle);
-    float a = (logf(MIN_CONE_STEPSIZE()) - logf(log1p_c)) / log1p_c;
-    float b = (logf(MAX_CONE_STEPSIZE()) - logf(log1p_c)) / log1p_c;
-    float at = expf(a * log1p_c), bt = expf(b * log1p_c);
-    if (t <= at) return (t - at) / MIN_CONE_STEPSIZE() + a;
-    else if (t <= bt) return logf(t) / log1p_c;
-    else return (t - bt) / MAX_CONE_STEPSIZE() + b;
-}
-NGP_HD float from_stepping_space(float n, float cone_angle) {
-    if (cone_angle <= 1e-5f) return n * MIN_CONE_STEPSIZE();
-    float log1p_c = logf(1.0f + cone_angle);
-    float a = (logf(MIN_CONE_STEPSIZE()) - logf(log1p_c)) / log1p_c;
-    float b = (logf(MAX_CONE_STEPSIZE()) - logf(log1p_c)) / log1p_c;
-    float at = expf(a * log1p_c), bt = expf(b * log1p_c);
-    if (n <= a) return (n - a) * MIN_CONE_STEPSIZE() + at;
-    else if (n <= b) return expf(n * log1p_c);
-    else return (n - b) * MAX_CONE_STEPSIZE() + bt;
-}
-NGP_HD float advance_n_steps(float t, float cone_angle, float n) { return from_stepping_space(to_stepping_space(t, cone_angle) + n, cone_angle); }
-NGP_HD float calc_dt(float t, float cone_angle) { return advance_n_steps(t, cone_angle, 1.0f) - t; }
-
+// ---- stepping (what testbed_nerf.cu:124-184 computes; evaluated through struct Cone below) ----
+// logf / expf come from include/ngp_b200_math.h: explicitly rounded fp32, the same source the CPU oracle compiles, so the
+// cell a step falls in is the same on both sides (north_star: occupancy traversal bit-exact, cone angle included).
 // t / MIN_CONE_STEPSIZE() without the generic IEEE-division sequence: q = t * (1/S) refined by one exact-residual FMA step
 // is the correctly rounded quotient; verified EXHAUSTIVELY against t / S for every float in [1e-30, 2048)
 // (tools/verify_fast_div.c: 1 157 627 904 values, 0 mismatches); outside that range the plain division is used.
@@ -77,22 +57,22 @@ struct Cone {
     float angle, log1p_c, a, b, at, bt;
     NGP_HD explicit Cone(float cone_angle) : angle(cone_angle), log1p_c(0.f), a(0.f), b(0.f), at(0.f), bt(0.f) {
         if (cone_angle <= 1e-5f) return;
-        log1p_c = logf(1.0f + cone_angle);
-        a = (logf(MIN_CONE_STEPSIZE()) - logf(log1p_c)) / log1p_c;
-        b = (logf(MAX_CONE_STEPSIZE()) - logf(log1p_c)) / log1p_c;
-        at = expf(a * log1p_c); bt = expf(b * log1p_c);
+        log1p_c = ngp_logf(1.0f + cone_angle);
+        a = (ngp_logf(MIN_CONE_STEPSIZE()) - ngp_logf(log1p_c)) / log1p_c;
+        b = (ngp_logf(MAX_CONE_STEPSIZE()) - ngp_logf(log1p_c)) / log1p_c;
+        at = ngp_expf(a * log1p_c); bt = ngp_expf(b * log1p_c);
     }
 };
 NGP_HD float to_stepping_space(float t, const Cone& c) {
     if (c.angle <= 1e-5f) return div_by_stepsize(t);   // == t / MIN_CONE_STEPSIZE(), bit for bit
     if (t <= c.at) return (t - c.at) / MIN_CONE_STEPSIZE() + c.a;
-    else if (t <= c.bt) return logf(t) / c.log1p_c;
+    else if (t <= c.bt) return ngp_logf(t) / c.log1p_c;
     else return (t - c.bt) / MAX_CONE_STEPSIZE() + c.b;
 }
 NGP_HD float from_stepping_space(float n, const Cone& c) {
     if (c.angle <= 1e-5f) return n * MIN_CONE_STEPSIZE();
     if (n <= c.a) return (n - c.a) * MIN_CONE_STEPSIZE() + c.at;
-    else if (n <= c.b) return expf(n * c.log1p_c);
+    else if (n <= c.b) return ngp_expf(n * c.log1p_c);
     else return (n - c.b) * MAX_CONE_STEPSIZE() + c.bt;
 }
 NGP_HD float advance_n_steps(float t, const Cone& c, float n) { return from_stepping_space(to_stepping_space(t, c) + n, c); }
@@ -159,14 +139,6 @@ NGP_HD float distance_to_next_voxel(V3 pos, V3 dir, V3 idir, float res) {
     float t = fminf(fminf(tx, ty), tz);
     return fmaxf(t / res, 0.0f);
 }
-NGP_HD float advance_to_next_voxel(float t, float cone, V3 pos, V3 dir, V3 idir, uint32_t mip) {
-    float res = scalbnf((float)NERF_GRIDSIZE, -(int)mip);
-    float t_target = t + distance_to_next_voxel(pos, dir, idir, res);
-    t = to_stepping_space(t, cone);
-    t_target = to_stepping_space(t_target, cone);
-    return from_stepping_space(t + ceilf(fmaxf(t_target - t, 0.5f)), cone);
-}
-
 NGP_HD float advance_to_next_voxel(float t, const Cone& cone, V3 pos, V3 dir, V3 idir, uint32_t mip) {
     // res = scalbnf(128, -mip) is a power of two: the division by it in distance_to_next_voxel is the exact multiplication by 2^(mip-7)
     const float res = pow2i(7 - (int)mip), inv_res = pow2i((int)mip - 7);
@@ -218,9 +190,12 @@ NGP_HD float srgb_to_linear(float s) { return s <= 0.04045f ? s / 12.92f : powf(
 NGP_HD float linear_to_srgb(float l) { return l < 0.0031308f ? 12.92f * l : 1.055f * powf(l, 0.41666f) - 0.055f; }
 
 // ---- network output activations (testbed_nerf.cu:317-387) ----
+// density -> alpha -> transmittance decide how many samples of a ray survive compaction (T < 1e-4 cut-off), an integer
+// result compared bit-exact with the oracle: exp() on that chain is ngp_expf (shared source); colours use the library.
+NGP_HD float alpha_from_density(float density, float dt) { return 1.f - ngp_expf(-density * dt); }
 NGP_HD float logistic(float x) { return 1.0f / (1.0f + expf(-x)); }
 NGP_HD float network_to_density(float v, int act) {
-    switch (act) { case ACT_NONE: return v; case ACT_RELU: return v > 0.f ? v : 0.f; case ACT_LOGISTIC: return logistic(v); default: return expf(v); }
+    switch (act) { case ACT_NONE: return v; case ACT_RELU: return v > 0.f ? v : 0.f; case ACT_LOGISTIC: return logistic(v); default: return ngp_expf(v); }
 }
 NGP_HD float network_to_density_derivative(float v, int act) {
     switch (act) { case ACT_NONE: return 1.f; case ACT_RELU: return v > 0.f ? 1.f : 0.f;

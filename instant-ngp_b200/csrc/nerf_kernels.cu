@@ -873,7 +873,7 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_forward_kernel(uint32_t n_ray
             const V3 rgb = v3(network_to_rgb(o[0], cfg.rgb_activation), network_to_rgb(o[1], cfg.rgb_activation), network_to_rgb(o[2], cfg.rgb_activation));
             const float dt = unwarp_dt(__ldg(cin + (size_t)cn * 7 + 3));
             const float density = network_to_density(o[3], cfg.density_activation);
-            const float alpha = 1.f - expf(-density * dt);
+            const float alpha = alpha_from_density(density, dt);
             const float weight = alpha * T;
             rgb_ray = rgb_ray + weight * rgb;
             T *= (1.f - alpha);
@@ -948,7 +948,7 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_backward_kernel(uint32_t n_ra
         float o[4]; load_out4(no + (size_t)j * 4, o);
         const V3 rgb = v3(network_to_rgb(o[0], cfg.rgb_activation), network_to_rgb(o[1], cfg.rgb_activation), network_to_rgb(o[2], cfg.rgb_activation));
         const float density = network_to_density(o[3], cfg.density_activation);
-        const float alpha = 1.f - expf(-density * dt);
+        const float alpha = alpha_from_density(density, dt);
         const float weight = alpha * T;
         rgb_ray2 = rgb_ray2 + weight * rgb;
         T *= (1.f - alpha);
@@ -1018,7 +1018,7 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_forward_group_kernel(uint32_t
                 rgb = v3(network_to_rgb(o[0], cfg.rgb_activation), network_to_rgb(o[1], cfg.rgb_activation), network_to_rgb(o[2], cfg.rgb_activation));
                 const float dt = unwarp_dt(dtw);
                 const float density = network_to_density(o[3], cfg.density_activation);
-                alpha = 1.f - expf(-density * dt);
+                alpha = alpha_from_density(density, dt);
             }
             const uint32_t n = min(G, numsteps - c0);
             float Tb = 0.f; uint32_t done = 0;
@@ -1119,7 +1119,7 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_backward_group_kernel(uint32_
             { const __half* h = reinterpret_cast<const __half*>(&raw); o[0] = __half2float(h[0]); o[1] = __half2float(h[1]); o[2] = __half2float(h[2]); o[3] = __half2float(h[3]); }
             rgb = v3(network_to_rgb(o[0], cfg.rgb_activation), network_to_rgb(o[1], cfg.rgb_activation), network_to_rgb(o[2], cfg.rgb_activation));
             const float density = network_to_density(o[3], cfg.density_activation);
-            alpha = 1.f - expf(-density * dt);
+            alpha = alpha_from_density(density, dt);
         }
         const float weight = alpha * Tb, T_after = Tb * (1.f - alpha);   // the chain's own products, from its stored state
         const V3 wr = weight * rgb;                                        // 0 on lanes past the end
@@ -1299,7 +1299,7 @@ __global__ void composite_kernel(uint32_t n_alive, uint32_t current_step, Aabb a
         const V3 pos = unwarp_position(v3(in[0], in[1], in[2]), aabb);
         const float T = 1.f - c.w;
         const float dt = unwarp_dt(in[3]);
-        const float alpha = 1.f - expf(-network_to_density(o[3], density_act) * dt);
+        const float alpha = alpha_from_density(network_to_density(o[3], density_act), dt);
         const float weight = alpha * T;
         c.x += network_to_rgb(o[0], rgb_act) * weight; c.y += network_to_rgb(o[1], rgb_act) * weight; c.z += network_to_rgb(o[2], rgb_act) * weight;
         c.w += weight;

@@ -5,10 +5,23 @@
 // what the CUDA kernels (compiled with --fmad=false) do as well, so occupancy traversal is bit-exact for
 // cone_angle == 0 (no transcendental in the stepping) and the integer paths are bit-exact always.
 #include "ngp_ref_nerf.h"
+#include "../include/ngp_b200_math.h"
 #include <cmath>
 #include <cstring>
 #include <vector>
 #include <algorithm>
+
+// Transcendentals that feed integer decisions (cell of a marcher step, transmittance cut-off of the compositor):
+// math mode 1 (default) evaluates them with the explicitly rounded fp32 logf/expf of include/ngp_b200_math.h — the same
+// source the CUDA kernels compile, so GPU and oracle agree bit for bit; math mode 0 uses libm, which is what the
+// reference's own helper code compiled here with g++ uses (tests/test_oracle_pins.py pins the FORMULAS in that mode).
+static int g_math_mode = 1;
+extern "C" void ref_set_math_mode(int shared) { g_math_mode = shared ? 1 : 0; }
+extern "C" int ref_get_math_mode() { return g_math_mode; }
+extern "C" float ref_shared_logf(float x) { return ngp_logf(x); }
+extern "C" float ref_shared_expf(float x) { return ngp_expf(x); }
+static inline float m_logf(float x) { return g_math_mode ? ngp_logf(x) : logf(x); }
+static inline float m_expf(float x) { return g_math_mode ? ngp_expf(x) : expf(x); }
 
 static inline float h2f(uint16_t h) { _Float16 v; memcpy(&v, &h, 2); return (float)v; }
 static inline uint16_t f2h(float f) { _Float16 v = (_Float16)f; uint16_t h; memcpy(&h, &v, 2); return h; }
@@ -94,22 +107,22 @@ extern "C" float ref_linear_to_srgb(float l) { return l < 0.0031308f ? 12.92f * 
 // ---- stepping (testbed_nerf.cu:124-184) ----
 extern "C" float ref_to_stepping_space(float t, float cone_angle) {
     if (cone_angle <= 1e-5f) return t / MIN_CONE_STEPSIZE();
-    float log1p_c = logf(1.0f + cone_angle);
-    float a = (logf(MIN_CONE_STEPSIZE()) - logf(log1p_c)) / log1p_c;
-    float b = (logf(MAX_CONE_STEPSIZE()) - logf(log1p_c)) / log1p_c;
-    float at = expf(a * log1p_c), bt = expf(b * log1p_c);
+    float log1p_c = m_logf(1.0f + cone_angle);
+    float a = (m_logf(MIN_CONE_STEPSIZE()) - m_logf(log1p_c)) / log1p_c;
+    float b = (m_logf(MAX_CONE_STEPSIZE()) - m_logf(log1p_c)) / log1p_c;
+    float at = m_expf(a * log1p_c), bt = m_expf(b * log1p_c);
     if (t <= at) return (t - at) / MIN_CONE_STEPSIZE() + a;
-    else if (t <= bt) return logf(t) / log1p_c;
+    else if (t <= bt) return m_logf(t) / log1p_c;
     else return (t - bt) / MAX_CONE_STEPSIZE() + b;
 }
 extern "C" float ref_from_stepping_space(float n, float cone_angle) {
     if (cone_angle <= 1e-5f) return n * MIN_CONE_STEPSIZE();
-    float log1p_c = logf(1.0f + cone_angle);
-    float a = (logf(MIN_CONE_STEPSIZE()) - logf(log1p_c)) / log1p_c;
-    float b = (logf(MAX_CONE_STEPSIZE()) - logf(log1p_c)) / log1p_c;
-    float at = expf(a * log1p_c), bt = expf(b * log1p_c);
+    float log1p_c = m_logf(1.0f + cone_angle);
+    float a = (m_logf(MIN_CONE_STEPSIZE()) - m_logf(log1p_c)) / log1p_c;
+    float b = (m_logf(MAX_CONE_STEPSIZE()) - m_logf(log1p_c)) / log1p_c;
+    float at = m_expf(a * log1p_c), bt = m_expf(b * log1p_c);
     if (n <= a) return (n - a) * MIN_CONE_STEPSIZE() + at;
-    else if (n <= b) return expf(n * log1p_c);
+    else if (n <= b) return m_expf(n * log1p_c);
     else return (n - b) * MAX_CONE_STEPSIZE() + bt;
 }
 extern "C" float ref_advance_n_steps(float t, float c, float n) { return ref_from_stepping_space(ref_to_stepping_space(t, c) + n, c); }
@@ -333,7 +346,7 @@ extern "C" void ref_generate_grid_samples_nonuniform(uint32_t n_elements, uint64
 static inline float logistic(float x) { return 1.0f / (1.0f + expf(-x)); }
 static inline float network_to_density(float v, int act) {   // testbed_nerf.cu:354-363
     switch (act) { case REF_ACT_NONE: return v; case REF_ACT_RELU: return v > 0.f ? v : 0.f;
-        case REF_ACT_LOGISTIC: return logistic(v); default: return expf(v); }
+        case REF_ACT_LOGISTIC: return logistic(v); default: return m_expf(v); }
 }
 static inline float network_to_density_derivative(float v, int act) {   // :365-378
     switch (act) { case REF_ACT_NONE: return 1.f; case REF_ACT_RELU: return v > 0.f ? 1.f : 0.f;
@@ -521,7 +534,7 @@ extern "C" void ref_compute_loss(uint32_t n_rays, const RefAabb* aabb, uint32_t 
                         network_to_rgb(h2f(no[cn * 4 + 2]), cfg->rgb_activation));
             float dt = unwarp_dt(cin[cn * 7 + 3]);
             float density = network_to_density(h2f(no[cn * 4 + 3]), cfg->density_activation);
-            float alpha = 1.f - expf(-density * dt);
+            float alpha = 1.f - m_expf(-density * dt);
             float weight = alpha * T;
             rgb_ray = rgb_ray + weight * rgb;
             T *= (1.f - alpha);
@@ -573,7 +586,7 @@ extern "C" void ref_compute_loss(uint32_t n_rays, const RefAabb* aabb, uint32_t 
             float o0 = h2f(no[j * 4]), o1 = h2f(no[j * 4 + 1]), o2 = h2f(no[j * 4 + 2]), o3 = h2f(no[j * 4 + 3]);
             V3 rgb = v3(network_to_rgb(o0, cfg->rgb_activation), network_to_rgb(o1, cfg->rgb_activation), network_to_rgb(o2, cfg->rgb_activation));
             float density = network_to_density(o3, cfg->density_activation);
-            float alpha = 1.f - expf(-density * dt);
+            float alpha = 1.f - m_expf(-density * dt);
             float weight = alpha * T;
             rgb_ray2 = rgb_ray2 + weight * rgb;
             T *= (1.f - alpha);
@@ -674,7 +687,7 @@ extern "C" void ref_render_nerf(const RefRenderCfg* c, const RefNerfNetCfg* net,
             V3 pos = unwarp_position(wp, &c->train_aabb);
             float T = 1.f - a;
             float dtu = unwarp_dt(coord[3]);
-            float alpha = 1.f - expf(-network_to_density(h2f(outh[3]), c->density_activation) * dtu);
+            float alpha = 1.f - m_expf(-network_to_density(h2f(outh[3]), c->density_activation) * dtu);
             float weight = alpha * T;
             r += network_to_rgb(h2f(outh[0]), c->rgb_activation) * weight;
             g += network_to_rgb(h2f(outh[1]), c->rgb_activation) * weight;

@@ -13,7 +13,16 @@ G = np.load(os.path.join(os.path.dirname(__file__), "golden", "reference_helpers
 
 @pytest.fixture(scope="module")
 def L(ref):
+    """the oracle in math mode 0: libm logf/expf, i.e. what the reference's own helper code compiled with g++ evaluates — this
+    pins the FORMULAS; mode 1 (the default everywhere else) swaps in the shared explicitly rounded logf/expf that the CUDA
+    kernels compile too (include/ngp_b200_math.h), checked against libm in test_shared_logf_expf_vs_libm"""
     l = ref.lib()
+    l.ref_set_math_mode(0)
+    yield from _bind(l)
+    l.ref_set_math_mode(1)
+
+
+def _bind(l):
     f32, u32, i32, vp = C.c_float, C.c_uint32, C.c_int, C.c_void_p
     for name, res, args in [("ref_advance_to_next_voxel", f32, [f32, f32, vp, vp, u32]), ("ref_warp_dt", f32, [f32]), ("ref_unwarp_dt", f32, [f32]),
                             ("ref_network_to_rgb", f32, [f32, i32]), ("ref_network_to_rgb_derivative", f32, [f32, i32]),
@@ -21,7 +30,7 @@ def L(ref):
                             ("ref_mip_from_pos", u32, [vp, u32]), ("ref_mip_from_dt", u32, [f32, vp, u32]), ("ref_cascaded_grid_idx_at", u32, [vp, u32]),
                             ("ref_density_grid_occupied_at", i32, [vp, vp, u32]), ("ref_aabb_contains", i32, [vp, vp])]:
         getattr(l, name).restype = res; getattr(l, name).argtypes = args
-    return l
+    yield l
 
 
 def _same(a, b):
@@ -92,3 +101,31 @@ def test_dt_warp_activations_and_losses(ref, L):
         for k in range(len(lg)):
             L.ref_loss_and_gradient(ref.P(G["loss_target"][k]), ref.P(G["loss_pred"][k]), lt, ref.P(lg[k]))
         assert _same(lg, G[f"loss_{lt}"]), lt
+
+
+def _ulp_diff(a, b):
+    ia = a.view(np.int32).astype(np.int64); ib = b.view(np.int32).astype(np.int64)
+    ia = np.where(ia < 0, -(ia & 0x7fffffff), ia); ib = np.where(ib < 0, -(ib & 0x7fffffff), ib)
+    return np.abs(ia - ib)
+
+
+def test_shared_logf_expf_vs_libm(ref):
+    """include/ngp_b200_math.h (compiled into the oracle AND the CUDA library from the same source): within 2 ulp of the
+    correctly rounded result over the ranges the marcher and the compositor feed it, exact IEEE conventions at the edges"""
+    l = ref.lib()
+    l.ref_shared_logf.restype = C.c_float; l.ref_shared_logf.argtypes = [C.c_float]
+    l.ref_shared_expf.restype = C.c_float; l.ref_shared_expf.argtypes = [C.c_float]
+    rng = np.random.default_rng(7)
+    x = np.concatenate([np.exp(rng.uniform(-80, 80, 20000)), rng.uniform(0.5, 2.0, 20000), rng.uniform(1e-3, 64.0, 20000),
+                        np.array([1.0, 1.0 + 1.0 / 256.0, 1.73205080757 / 1024, 1e-38, 1e-42, 3.4e38])]).astype(np.float32)
+    got = np.array([l.ref_shared_logf(float(v)) for v in x], np.float32)
+    want = np.log(x.astype(np.float64)).astype(np.float32)
+    assert _ulp_diff(got, want).max() <= 2
+    y = np.concatenate([rng.uniform(-100, 88, 40000), rng.uniform(-1, 1, 20000), np.array([0.0, -0.0, 88.7, -103.9, -87.5])]).astype(np.float32)
+    got = np.array([l.ref_shared_expf(float(v)) for v in y], np.float32)
+    want = np.exp(y.astype(np.float64)).astype(np.float32)
+    normal = want > 1.2e-38
+    assert _ulp_diff(got[normal], want[normal]).max() <= 2
+    assert np.abs(got[~normal].astype(np.float64) - want[~normal].astype(np.float64)).max() <= 2 * 1.4e-45 + 1e-44
+    assert l.ref_shared_expf(100.0) == np.inf and l.ref_shared_expf(-200.0) == 0.0 and l.ref_shared_logf(0.0) == -np.inf
+    assert np.isnan(l.ref_shared_logf(-1.0)) and l.ref_shared_logf(1.0) == 0.0 and l.ref_shared_expf(0.0) == 1.0
