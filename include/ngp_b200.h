@@ -31,6 +31,13 @@ uint64_t ngp_kernel_launch_count(void);
 void ngp_profile_enable(int on);
 int ngp_profile_report(char* buf, uint64_t buf_size, int reset);
 
+/* Roofline denominators of the hash-grid kernels, measured on the current device (no reference
+ * counterpart — the reference publishes no roofline): random 4-byte gathers per second with 32 loads in flight per
+ * thread over a buffer of `buffer_bytes` (the table size: L2-resident when it fits), and scattered
+ * red.global.add.f16x2 lanes per second (`vec` = 4-byte entries per lane: 1, 2 or 4).  Median of `reps` launches. */
+int ngp_microbench_l2_gather(void* stream, uint64_t buffer_bytes, uint32_t reps, double* gathers_per_s);
+int ngp_microbench_l2_red(void* stream, uint64_t buffer_bytes, int32_t vec, uint32_t reps, double* lanes_per_s);
+
 /* activation layouts for encoder outputs / MLP inputs */
 enum { NGP_LAYOUT_ROWMAJOR = 0, /* [n][C] fp16 ("AoS", tcnn::RM with one sample per row) */
        NGP_LAYOUT_BLK8 = 1      /* 8x8 fp16 core matrices, the tcgen05 no-swizzle operand layout */ };

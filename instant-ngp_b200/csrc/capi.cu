@@ -49,6 +49,17 @@ int ngp_profile_report(char* buf, uint64_t buf_size, int reset) {
     NGP_API_END
 }
 
+int ngp_microbench_l2_gather(void* stream, uint64_t buffer_bytes, uint32_t reps, double* out) {
+    NGP_API_BEGIN NGP_CHECK(out, "null argument"); require_device();
+    *out = microbench_l2_gather(S(stream), buffer_bytes, reps);
+    NGP_API_END
+}
+int ngp_microbench_l2_red(void* stream, uint64_t buffer_bytes, int32_t vec, uint32_t reps, double* out) {
+    NGP_API_BEGIN NGP_CHECK(out, "null argument"); require_device();
+    *out = microbench_l2_red(S(stream), buffer_bytes, vec, reps);
+    NGP_API_END
+}
+
 // ---- encoding ----
 int ngp_encoding_create(const char* json, uint32_t n_dims, ngp_encoding_t* out) {
     NGP_API_BEGIN

@@ -213,12 +213,33 @@ NGP_D void red_add_entry(__half* p, float w, const float* d) {
 // reduction (fp32) and only the first lane of a run issues reductions.  Fine levels (every lane its own cell) take the direct path.
 
 template <uint32_t D, uint32_t F>
-NGP_D void scatter_corners(const LevelCorners<D>& lc, __half* __restrict__ gl, const float (*v)[F]) {
+NGP_D void scatter_corners(const LevelCorners<D>& lc, __half* __restrict__ gl, const float (*v)[F], bool wide) {
     constexpr uint32_t NC = 1u << D;
-    if (F <= 4) {
+    if (F == 2 && wide) {
+        // Scattered reductions cost one LSU slot per LANE whatever their width (measured: merging aligned x-neighbour pairs into
+        // one 8-byte RED took 0.136 -> 0.106 ms).  The two corners along x are one entry apart (hashed levels: x enters the XOR
+        // unmultiplied; dense levels: stride 1), so they sit in the same aligned group of FOUR entries (16 bytes) unless x % 4 == 3:
+        // one red.v4.f16x2 carries both in 3 of 4 cases (the aligned pair only in 1 of 2), the two idle slots add +0.
+#pragma unroll
+        for (uint32_t k = 0; k < NC; k += 2) {
+            const uint32_t ia = lc.index(k), ib = lc.index(k + 1);
+            if ((ia ^ ib) < 4u) {
+                const uint32_t sa = ia & 3u, sb = ib & 3u;
+                float o[8];
+#pragma unroll
+                for (uint32_t sl = 0; sl < 4; ++sl) {
+                    o[2 * sl] = (sa == sl ? v[k][0] : 0.0f) + (sb == sl ? v[k + 1][0] : 0.0f);
+                    o[2 * sl + 1] = (sa == sl ? v[k][1 % F] : 0.0f) + (sb == sl ? v[k + 1][1 % F] : 0.0f);
+                }
+                red_add_h8(gl + (size_t)(ia & ~3u) * F, o[0], o[1], o[2], o[3], o[4], o[5], o[6], o[7]);
+            } else {
+                red_add_entry<F>(gl + (size_t)ia * F, 1.0f, v[k]);
+                red_add_entry<F>(gl + (size_t)ib * F, 1.0f, v[k + 1]);
+            }
+        }
+    } else if (F <= 4) {
         // The two corners along x are table neighbours (index ^ 1) whenever the cell's x is even (hashed: the x term enters the
-        // XOR unmultiplied) or the dense index is even: they then go out as ONE vector reduction.  Scattered reductions cost
-        // one LSU slot per lane, so this removes a quarter of them (measured: 0.136 -> 0.106 ms per 2^18 samples).
+        // XOR unmultiplied) or the dense index is even: they then go out as ONE vector reduction.
 #pragma unroll
         for (uint32_t k = 0; k < NC; k += 2) {
             const uint32_t ia = lc.index(k), ib = lc.index(k + 1);
@@ -242,7 +263,7 @@ NGP_D void scatter_corners(const LevelCorners<D>& lc, __half* __restrict__ gl, c
 
 template <uint32_t D, uint32_t F>
 __global__ void __launch_bounds__(256) grid_backward_kernel(const GridLayout g, const float* __restrict__ x, uint32_t x_stride, uint32_t n,
-                                                            const __half* __restrict__ dy, int dy_layout, __half* __restrict__ grad, uint32_t chunk0, uint32_t agg_max_runs) {
+                                                            const __half* __restrict__ dy, int dy_layout, __half* __restrict__ grad, uint32_t chunk0, uint32_t agg_max_runs, bool wide) {
     constexpr uint32_t LPC = 8 / F;
     constexpr uint32_t NC = 1u << D;
     const uint32_t row = blockIdx.x * blockDim.x + threadIdx.x, chunk = chunk0 + blockIdx.y, lane = threadIdx.x & 31u;
@@ -295,9 +316,9 @@ __global__ void __launch_bounds__(256) grid_backward_kernel(const GridLayout g, 
 #pragma unroll
                     for (uint32_t f = 0; f < F; ++f) { const float t = __shfl_down_sync(0xffffffffu, v[k][f], o); if (take) v[k][f] += t; }
             }
-            if (!same && any) scatter_corners<D, F>(lc, gl, v);
+            if (!same && any) scatter_corners<D, F>(lc, gl, v, wide);
         } else if (any) {
-            scatter_corners<D, F>(lc, gl, v);
+            scatter_corners<D, F>(lc, gl, v, wide);
         }
     }
 }
@@ -396,6 +417,10 @@ void grid_forward(cudaStream_t s, const GridLayout& g, const __half* table, cons
 
 // runs per warp up to which a level is aggregated (0 = never); NGP_AGG_MAX_RUNS overrides for experiments.  Measured (tools/sweep_agg.sh,
 // grid_backward ms per 2^18 samples, synthetic scene / fox): 0: 0.119 / 0.359, 4: 0.109 / 0.216, 8: 0.113 / 0.184, 12: 0.108 / 0.163, 16: 0.126 / 0.141
+static bool red_wide() {   // NGP_RED_V4=0: aligned-pair (8-byte) merging only, for A/B measurements
+    static const bool v = [] { const char* e = getenv("NGP_RED_V4"); return e ? atoi(e) != 0 : true; }();
+    return v;
+}
 static uint32_t agg_max_runs() {
     static const uint32_t v = [] { const char* e = getenv("NGP_AGG_MAX_RUNS"); return e ? (uint32_t)atoi(e) : 12u; }();
     return v;
@@ -406,7 +431,7 @@ void grid_backward(cudaStream_t s, const GridLayout& g, const float* x, uint32_t
     if (n == 0) return;
     NGP_PROFILE_SCOPE(s, "grid_backward", n);
     const dim3 blocks(div_round_up(n, 256), g.padded_width / 8, 1);
-    GRID_DISPATCH(grid_backward_kernel, g, x, x_stride, n, dy, dy_layout, grad, 0u, agg_max_runs());
+    GRID_DISPATCH(grid_backward_kernel, g, x, x_stride, n, dy, dy_layout, grad, 0u, agg_max_runs(), red_wide());
 }
 
 // the same pass restricted to 8-feature chunks [chunk0, chunk0 + n_chunks): the data-parallel step launches it chunk by chunk
@@ -416,7 +441,7 @@ void grid_backward_chunks(cudaStream_t s, const GridLayout& g, const float* x, u
     if (n == 0 || n_chunks == 0) return;
     NGP_PROFILE_SCOPE(s, "grid_backward", n);
     const dim3 blocks(div_round_up(n, 256), n_chunks, 1);
-    GRID_DISPATCH(grid_backward_kernel, g, x, x_stride, n, dy, dy_layout, grad, chunk0, agg_max_runs());
+    GRID_DISPATCH(grid_backward_kernel, g, x, x_stride, n, dy, dy_layout, grad, chunk0, agg_max_runs(), red_wide());
 }
 
 void grid_backward_input(cudaStream_t s, const GridLayout& g, const __half* table, const float* x, uint32_t x_stride,

@@ -3,6 +3,9 @@
 #include "network.h"
 #include <cmath>
 #include <cstring>
+#include <cstdio>
+#include <cstdlib>
+#include <algorithm>
 
 namespace ngp {
 
@@ -207,7 +210,8 @@ void Optimizer::update_hyperparams(const Json& j) {
 }
 
 Trainer::Trainer(uint64_t n, uint64_t n_matrix, const Json& optimizer_cfg) : n_params(n), n_matrix_params(n_matrix), opt(optimizer_cfg) {
-    NGP_CUDA_CHECK(cudaMalloc(&master, n * 4)); NGP_CUDA_CHECK(cudaMalloc(&params, n * 2)); NGP_CUDA_CHECK(cudaMalloc(&grads, n * 2));
+    const uint64_t n_al = next_multiple(n, 128);   // grads start 256-byte aligned behind params in the same allocation (one L2 window covers both)
+    NGP_CUDA_CHECK(cudaMalloc(&master, n * 4)); NGP_CUDA_CHECK(cudaMalloc(&params, n_al * 2 * 2)); grads = params + n_al;
     NGP_CUDA_CHECK(cudaMalloc(&m, n * 4)); NGP_CUDA_CHECK(cudaMalloc(&v, n * 4)); NGP_CUDA_CHECK(cudaMalloc(&steps, n * 4));
     NGP_CUDA_CHECK(cudaMemset(m, 0, n * 4)); NGP_CUDA_CHECK(cudaMemset(v, 0, n * 4)); NGP_CUDA_CHECK(cudaMemset(steps, 0, n * 4));
     NGP_CUDA_CHECK(cudaMemset(grads, 0, n * 2));
@@ -219,7 +223,30 @@ Trainer::Trainer(uint64_t n, uint64_t n_matrix, const Json& optimizer_cfg) : n_p
 
 Trainer::~Trainer() {
     if (inference_params && inference_params != params) cudaFree(inference_params);
-    cudaFree(master); cudaFree(params); cudaFree(grads); cudaFree(m); cudaFree(v); cudaFree(steps); if (ema) cudaFree(ema);
+    cudaFree(master); cudaFree(params); cudaFree(m); cudaFree(v); cudaFree(steps); if (ema) cudaFree(ema);
+}
+
+uint64_t Trainer::apply_l2_policy(cudaStream_t s) {
+    if (l2_tried && l2_stream == s) return l2_window_bytes;
+    l2_tried = true; l2_stream = s; l2_window_bytes = 0;
+    if (const char* e = getenv("NGP_L2_PERSIST")) if (atoi(e) == 0) return 0;
+    int dev = 0, max_persist = 0, max_window = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+    cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, dev);
+    cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, dev);
+    if (max_persist <= 0 || max_window <= 0) return 0;
+    const uint64_t want = (uint64_t)((const char*)(grads + n_params) - (const char*)params);
+    const uint64_t window = std::min<uint64_t>(want, (uint64_t)max_window), carve = std::min<uint64_t>(window, (uint64_t)max_persist);
+    if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, carve) != cudaSuccess) { cudaGetLastError(); return 0; }
+    cudaStreamAttrValue attr{};
+    attr.accessPolicyWindow.base_ptr = params; attr.accessPolicyWindow.num_bytes = window;
+    attr.accessPolicyWindow.hitRatio = (float)std::min(1.0, (double)carve / (double)window);
+    attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting; attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+    if (cudaStreamSetAttribute(s, cudaStreamAttributeAccessPolicyWindow, &attr) != cudaSuccess) { cudaGetLastError(); return 0; }
+    l2_window_bytes = window;
+    if (getenv("NGP_DEBUG")) fprintf(stderr, "[ngp] L2 policy: window %llu B, carve-out %llu B (max persisting %d, max window %d), hit ratio %.2f\n",
+                                     (unsigned long long)window, (unsigned long long)carve, max_persist, max_window, attr.accessPolicyWindow.hitRatio);
+    return window;
 }
 
 void Trainer::params_from_master(cudaStream_t s) {
@@ -234,6 +261,7 @@ void Trainer::optimizer_step(cudaStream_t s, float loss_scale) {
     h.optimize_matrix = opt.optimize_matrix; h.optimize_non_matrix = opt.optimize_non_matrix;
     h.ema_decay = opt.ema_decay; h.ema_step = opt.step_count + 1;
     h.clear_consumed_grads = 1; grid_grads_clean = true;
+    apply_l2_policy(s);
     adam_step(s, h, n_params, master, params, grads, m, v, steps, ema, ema ? inference_params : nullptr);
     ++opt.step_count;
     const uint32_t sc = opt.step_count;

@@ -89,6 +89,12 @@ struct Trainer {
     void params_from_master(cudaStream_t s);             // fp16 copies after initialize_params
     void optimizer_step(cudaStream_t s, float loss_scale);
     bool grid_grads_clean = false;   // the hash-table part of `grads` is all zero (left so by the last optimizer step)
+    // north_star: "tables pinned in B200's L2 via access-policy windows when they fit".  params and grads are ONE allocation
+    // [fp16 params | fp16 grads]; `s` gets a persisting access-policy window over it (hit ratio scaled to the carve-out when the
+    // table is larger), so the encoder's gathers and scatters stay in L2 while Adam streams ~300 MB of fp32 state past them
+    // (its loads / stores of that state carry evict-first hints).  Returns the bytes under the window (0: not applied).
+    uint64_t apply_l2_policy(cudaStream_t s);
+    uint64_t l2_window_bytes = 0; cudaStream_t l2_stream = nullptr; bool l2_tried = false;
 };
 
 }  // namespace ngp

@@ -97,4 +97,9 @@ void adam_step(cudaStream_t s, const AdamHyper& h, uint64_t n, float* master, __
                float* m, float* v, uint32_t* steps, float* ema_f32, __half* ema_half);
 void cast_f32_to_half(cudaStream_t s, const float* in, __half* out, uint64_t n);
 
+// Roofline denominators measured on this device (microbench.cu): random 4-byte gathers per second over an L2-sized buffer,
+// scattered fp16x2 reduction lanes per second (vec = 4-byte entries per lane: 1, 2 or 4)
+double microbench_l2_gather(cudaStream_t s, uint64_t buffer_bytes, uint32_t reps);
+double microbench_l2_red(cudaStream_t s, uint64_t buffer_bytes, int vec, uint32_t reps);
+
 }  // namespace ngp

@@ -55,8 +55,10 @@ __global__ void __launch_bounds__(256) adam_kernel(const AdamHyper h, const Adam
         // stream and lives on bytes in flight; only the optimizer state of touched entries is fetched behind the test
         const uint2 graw = __ldg(reinterpret_cast<const uint2*>(grads + i0));
         const uint2 praw = *reinterpret_cast<const uint2*>(params + i0);
+        // fp32 optimizer state is touched once per step and is ~10x the fp16 table: streaming (evict-first) accesses, so that it does
+        // not push the table (params + grads, under the persisting L2 window of Trainer::apply_l2_policy) out of L2
         float4 e4 = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (ema) e4 = *reinterpret_cast<const float4*>(ema + i0);
+        if (ema) e4 = __ldcs(reinterpret_cast<const float4*>(ema + i0));
         const __half* gh = reinterpret_cast<const __half*>(&graw);
         const __half* ph = reinterpret_cast<const __half*>(&praw);
         const bool matrix = i0 < h.n_matrix_params;       // n_matrix_params is a multiple of 4 (MLP layers are 16 x 64 blocks)
@@ -66,8 +68,8 @@ __global__ void __launch_bounds__(256) adam_kernel(const AdamHyper h, const Adam
         __half wh[4];
         *reinterpret_cast<uint2*>(wh) = praw;
         if (any) {
-            float4 w4 = *reinterpret_cast<float4*>(master + i0), m4 = *reinterpret_cast<float4*>(m + i0), v4 = *reinterpret_cast<float4*>(v + i0);
-            uint4 t4 = *reinterpret_cast<uint4*>(steps + i0);
+            float4 w4 = __ldcs(reinterpret_cast<const float4*>(master + i0)), m4 = __ldcs(reinterpret_cast<const float4*>(m + i0)), v4 = __ldcs(reinterpret_cast<const float4*>(v + i0));
+            uint4 t4 = __ldcs(reinterpret_cast<const uint4*>(steps + i0));
             float* w = reinterpret_cast<float*>(&w4); float* mm = reinterpret_cast<float*>(&m4); float* vv = reinterpret_cast<float*>(&v4);
             uint32_t* tt = reinterpret_cast<uint32_t*>(&t4);
 #pragma unroll
@@ -76,8 +78,8 @@ __global__ void __launch_bounds__(256) adam_kernel(const AdamHyper h, const Adam
                 adam_one(h, c, matrix, __half2float(gh[k]), w[k], mm[k], vv[k], tt[k], stepped);
                 wh[k] = stepped ? __float2half_rn(w[k]) : ph[k];
             }
-            *reinterpret_cast<float4*>(master + i0) = w4; *reinterpret_cast<float4*>(m + i0) = m4; *reinterpret_cast<float4*>(v + i0) = v4;
-            *reinterpret_cast<uint4*>(steps + i0) = t4;
+            __stcs(reinterpret_cast<float4*>(master + i0), w4); __stcs(reinterpret_cast<float4*>(m + i0), m4); __stcs(reinterpret_cast<float4*>(v + i0), v4);
+            __stcs(reinterpret_cast<uint4*>(steps + i0), t4);
             *reinterpret_cast<uint2*>(params + i0) = *reinterpret_cast<uint2*>(wh);
         }
         if (ema) {
@@ -88,8 +90,8 @@ __global__ void __launch_bounds__(256) adam_kernel(const AdamHyper h, const Adam
                 e[k] = (e[k] * h.ema_decay * c.ema_old_debias + __half2float(wh[k]) * (1.0f - h.ema_decay)) * c.inv_ema_new_debias;
                 eh[k] = __float2half_rn(e[k]);
             }
-            *reinterpret_cast<float4*>(ema + i0) = e4;
-            *reinterpret_cast<uint2*>(ema_half + i0) = *reinterpret_cast<uint2*>(eh);
+            __stcs(reinterpret_cast<float4*>(ema + i0), e4);
+            __stcs(reinterpret_cast<uint2*>(ema_half + i0), *reinterpret_cast<uint2*>(eh));
         }
         return;
     }
