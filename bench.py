@@ -122,6 +122,15 @@ def measured_peaks():
     return {"hbm_gbs": 6650.0, "tflops_burst": 1590.0, "tflops_sustained": 1400.0, "source": "fallback (B200_PROFILING.md)"}
 
 
+def profiled_instructions():
+    """warp instructions per unit of the issue-bound kernel groups, from the committed ncu capture (profiles/instructions.json), else {}"""
+    p = os.path.join(ROOT, "profiles", "instructions.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return json.load(f)
+    return {}
+
+
 def profiled_traffic():
     """dram bytes per launch of the top kernels from the committed ncu --set full capture (profiles/traffic.json), else {}"""
     p = os.path.join(ROOT, "profiles", "traffic.json")
@@ -132,47 +141,106 @@ def profiled_traffic():
 
 
 # ---------------------------------------------------------------------------------------------------------------
-# CPU arm (oracle): bounded sample of the same step
+# CPU arm (oracle): bounded sample of the same step, from the same trained state
 # ---------------------------------------------------------------------------------------------------------------
-def cpu_arm(steps, warmup, batch, n_views, res, log2T):
-    """Times `steps` Testbed::train steps of oracle/cpu_train.py (all host threads via OpenMP).
-    Sample: batch `batch` on `n_views` views of res x res of the same analytic scene and the same network config;
-    3 start-up steps, then the step counter is moved to the steady-state cadence (grid refresh every 16 steps over
-    128^3/2 cells, testbed.cu:4321 / testbed_nerf.cu:4146-4150) so that the refresh is amortised as in a long run."""
+def make_testbed(args, views=None):
+    """the CUDA Testbed on the workload of `args` (dataset resident in HBM, network initialised)"""
+    pyngp = importlib.import_module("instant-ngp_b200.pyngp")
+    scene = importlib.import_module("instant-ngp_b200.scene")
+    if views is None:
+        views = scene.make_views(args.views, args.res, args.res)            # pinned HOST buffers (like decoded images)
+    tb = pyngp.Testbed(pyngp.TestbedMode.Nerf)
+    tb.set_nerf_dataset(views, aabb_scale=1)
+    tb.reload_network_from_json(network_config(args.log2_hashmap_size))
+    return tb, views
+
+
+def trained_state(tb):
+    """host copy of everything a training step reads: parameters, optimizer moments are NOT needed for timing but the
+    occupancy grid, bitfield, counters and rays_per_batch are — oracle/cpu_train.CpuNerfTrainer.adopt_state() continues from it"""
+    import torch
+    torch.cuda.synchronize()
+    st = tb.stats
+    return {"master": tb.param_buffer(0).cpu().numpy().copy(), "params": tb.param_buffer(1).cpu().numpy().copy(),
+            "ema_h": tb.param_buffer(2).cpu().numpy().copy(),
+            "density_grid": tb.density_grid(0).cpu().numpy().copy(), "bitfield": tb.density_grid(1).cpu().numpy().copy(),
+            "mean_density": float(tb.debug_tensor("mean_density", torch.float32, 1).cpu().numpy()[0]),
+            "training_step": int(st.training_step), "rays_per_batch": int(st.rays_per_batch),
+            "measured_before": int(st.measured_batch_size_before_compaction), "measured": int(st.measured_batch_size)}
+
+
+def cpu_arm(args, views, state, steps, warmup, batch, pretrained_how):
+    """Times `steps` Testbed::train(batch) steps of oracle/cpu_train.py on all host threads (OpenMP), on the SAME views, network
+    and — through `state` — the same trained occupancy grid / parameters / rays_per_batch as the GPU arm.  The occupancy-grid
+    refresh (every 16th step at steady state, testbed.cu:4321) is timed once on its own and charged at 1/16 per step, so a
+    sample of a few steps carries the cadence of a long run."""
     from oracle import cpu_train, ref_api as ref
     cores = os.cpu_count() or 1
-    focal = 0.5 * res / math.tan(0.5 * 0.6911)
-    views = ref.synth_views(n_views, res, res, 4.0 * 0.33, focal)
-    tr = cpu_train.CpuNerfTrainer(network_config(log2T), views)
-    for _ in range(3):
-        tr.train(batch)
-    tr.training_step = 4096 - warmup      # the timed region starts on a grid-refresh step and holds one refresh per 16 steps
+    ref.lib().ref_set_num_threads(cores)                  # torchrun exports OMP_NUM_THREADS=1: set the count explicitly
+    threads = int(ref.lib().ref_get_max_threads())
+    tr = cpu_train.CpuNerfTrainer(network_config(args.log2_hashmap_size), views)
+    if state is not None:
+        tr.adopt_state(state)
+    # move to the first step after a refresh at the steady-state cadence (16), keeping the adopted grid
+    tr.training_step = max(tr.training_step, 4096) // 16 * 16 + 1
+    tr.rng_skip = 1 + tr.training_step * (1 << 32)
     for _ in range(warmup):
         tr.train(batch)
+    tr.training_step = tr.training_step // 16 * 16 + 1     # timed steps: none of them refreshes (steps <= 15)
     tr.timings.clear()
-    n = 0
+    n = 0; before = 0
     t0 = time.perf_counter()
     for _ in range(steps):
-        n += tr.train(batch)
+        n += tr.train(batch); before += tr.measured_before
     dt = time.perf_counter() - t0
-    return {"value": n / dt, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": f"{steps} steps of batch 2^{int(math.log2(batch))} ({n} samples, {dt:.1f} s) on {n_views} views {res}x{res}, "
-                      f"OpenMP over {cores} threads, steady-state grid cadence; samples before compaction/step ~{tr.measured_before}",
-            "ms_per_step": dt / steps * 1e3, "seconds": dt, "breakdown_s": {k: round(v, 3) for k, v in tr.timings.items()}}
+    t1 = time.perf_counter()
+    tr.update_density_grid(cpu_train.NC // 4, cpu_train.NC // 4)       # one steady-state refresh (128^3/2 cells, :4146-4150)
+    refresh = time.perf_counter() - t1
+    sec_per_step = dt / steps + refresh / 16.0
+    return {"value": (n / steps) / sec_per_step, "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": f"{steps} timed + {warmup} warm-up steps of batch 2^{int(math.log2(batch))} ({n} samples in {dt:.1f} s) + one occupancy-grid refresh "
+                      f"({refresh:.2f} s, charged 1/16 per step) on {len(views)} views {args.res}x{args.res}, T=2^{args.log2_hashmap_size}; OpenMP threads {threads} of "
+                      f"{cores} cores; state: {pretrained_how}; samples before compaction / trained sample {before / max(n, 1):.2f}",
+            "ms_per_step": sec_per_step * 1e3, "seconds": dt + refresh, "threads": threads,
+            "before_over_compacted": before / max(n, 1), "breakdown_s": {k: round(v, 3) for k, v in tr.timings.items()}}
 
 
 def run_reference(args):
+    """--impl reference: the reference has no CPU implementation and its CUDA build needs the absent tiny-cuda-nn submodule, so
+    this arm times the oracle's restatement of the same training step on the host cores, on the SAME workload as the own arm
+    (same views, network, batch) and from the same kind of trained state: when a GPU is present the state comes from `pretrain`
+    untimed steps of the CUDA Testbed (data synthesis and pre-training only; nothing of the product runs inside the timed
+    region), otherwise from a bounded number of CPU steps (said so in `config.workload`)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    steps = max(1, min(args.steps, 16)); warm = max(0, min(args.warmup, 2))
-    r = cpu_arm(steps, warm, 1 << 12, 8, 200, args.log2_hashmap_size)
+    steps = max(1, min(args.steps, args.cpu_steps)); warm = max(0, min(args.warmup, 1))
+    import torch
+    workload = workload_name(args)
+    if torch.cuda.is_available():
+        torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
+        tb, views = make_testbed(args)
+        for _ in range(args.pretrain):
+            tb.train(args.batch)
+        state = trained_state(tb)
+        how = f"{args.pretrain} untimed steps of the CUDA Testbed (same as the own arm), read back to the host"
+        del tb
+        torch.cuda.empty_cache()
+    else:
+        from oracle import ref_api as ref
+        focal = 0.5 * args.res / math.tan(0.5 * 0.6911)
+        views = ref.synth_views(args.views, args.res, args.res, 4.0 * 0.33, focal)
+        state = None; how = "untrained (no CUDA device to pre-train on)"; workload += "_UNTRAINED-STATE"
+    r = cpu_arm(args, views, state, steps, warm, args.batch, how)
     line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": steps, "warmup": warm,
             "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16 storage / f32 accumulate",
-            "data": "synthetic", "config": {"workload": workload_name(args), "note": "CPU restatement (oracle/) of the same training step; the reference has no CPU "
-                                            "implementation and its CUDA build needs the absent tiny-cuda-nn submodule"},
+            "data": "synthetic", "config": {"workload": workload, "global_batch": args.batch, "per_gpu_batch": args.batch,
+                                            "note": "CPU restatement (oracle/) of the same training step on the host cores of rank 0; the reference has no CPU "
+                                                    "implementation and its CUDA build needs the absent tiny-cuda-nn submodule",
+                                            "samples_before_compaction_per_trained_sample": r["before_over_compacted"], "omp_threads": r["threads"]},
             "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
-            "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+            "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0,
+            "breakdown_s": r["breakdown_s"]}
     print(json.dumps(line), flush=True)
 
 
@@ -210,16 +278,10 @@ def run_own(args):
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    pyngp = importlib.import_module("instant-ngp_b200.pyngp")
-    scene = importlib.import_module("instant-ngp_b200.scene")
     _lib = importlib.import_module("instant-ngp_b200._lib")
     lib = _lib.lib()
     cfg = network_config(args.log2_hashmap_size)
-
-    views = scene.make_views(args.views, args.res, args.res)            # pinned HOST buffers (like decoded images)
-    tb = pyngp.Testbed(pyngp.TestbedMode.Nerf)
-    tb.set_nerf_dataset(views, aabb_scale=1)
-    tb.reload_network_from_json(cfg)
+    tb, views = make_testbed(args)
     if world > 1:
         tb.enable_data_parallel(native=os.environ.get('NGP_DP_NATIVE', '1') == '1')
     batch = args.batch
@@ -230,12 +292,13 @@ def run_own(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    clk = ClockSampler(local).__enter__()      # runs from the untimed pre-training to the end of the e2e pass: every sample under the same training load
+    clk = ClockSampler(local).__enter__()      # runs from the untimed pre-training to the end of the timed windows: every sample under the same training load
     for _ in range(args.pretrain + args.warmup):
         tb.train(batch)
 
     def timed(steps, upload):
-        """K steps; returns (ms max over ranks, samples summed over ranks, samples before compaction, launches)"""
+        """EXACTLY `steps` steps between two CUDA events, barrier + synchronize on both sides; returns (ms max over ranks, samples
+        summed over ranks, samples before compaction, launches)"""
         n = 0; nb = 0
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         barrier()
@@ -257,11 +320,18 @@ def run_own(args):
             c = torch.tensor([n, nb], dtype=torch.float64, device="cuda"); dist.all_reduce(c); n, nb = int(c[0].item()), int(c[1].item())
         return ms, n, nb, launches
 
+    def windows(repeats, upload):
+        """the K-step window repeated back to back (a 20-step window is ~10 ms: one window is one clock sample and ~3 % noise);
+        the reported figure is the MEDIAN window, min / max are kept beside it"""
+        rows = [timed(args.steps, upload) for _ in range(repeats)]
+        rows.sort(key=lambda r: r[1] / r[0])
+        return rows[len(rows) // 2], rows
+
     ncu = os.environ.get("NGP_NCU") == "1"      # under `ncu --profile-from-start off`: capture only the timed steps
     if ncu:
         torch.cuda.profiler.start()
     t0 = time.time()
-    ms, n_samples, n_before, launches = timed(args.steps, upload=False)
+    (ms, n_samples, n_before, launches), rows = windows(1 if ncu else args.repeats, upload=False)
     t1 = time.time()
     if ncu:
         torch.cuda.profiler.stop()
@@ -269,59 +339,101 @@ def run_own(args):
     clocks = clk.summary([(t0, t1)])
     time.sleep(0.25)                            # let the stopped NVML poller go away
     timed(max(args.warmup, 3), upload=True)     # untimed warm-up of the upload path (copy stream, events, first pinned-page touches)
-    ms_e2e, n_e2e, _, _ = timed(args.steps, upload=True)
+    (ms_e2e, n_e2e, _, _), rows_e2e = windows(1 if ncu else max(3, args.repeats // 3), upload=True)
     view_bytes = int(views[0]["pixels"].numel())
     loss_steps = sum(1 for i in range(args.steps) if i % 16 == 0)
     d2h = 16 + 4.0 * loss_steps / args.steps
 
-    # per-kernel CUDA-event timing on the launching stream over a third pass of K steps (events add ~2 records per kernel,
+    # per-kernel CUDA-event timing on the launching stream over a separate pass of K steps (events add ~2 records per kernel,
     # so this pass is not the one `value` comes from)
     prefetch_hits = int(tb.prefetch_hits)
     tb.prefetch_rays = False            # kernels timed one at a time: no ray prefetch running beside them on the second stream
     lib.ngp_profile_enable(1)
     buf = C.create_string_buffer(1 << 16)
     lib.ngp_profile_report(buf, len(buf), 1)
-    timed(args.steps, upload=False)
+    prof_steps = max(args.steps, 32)
+    timed(prof_steps, upload=False)
     lib.ngp_profile_report(buf, len(buf), 1)
     lib.ngp_profile_enable(0)
+    tb.prefetch_rays = True
     prof = json.loads(buf.value.decode())
     peaks = measured_peaks()
     traffic = profiled_traffic()
+    inst = profiled_instructions()
+    # roofline denominators of the hash-grid kernels measured on this device, now
+    table_bytes = int(tb.n_params()) * 2
+    g = C.c_double(); r1 = C.c_double(); r2 = C.c_double()
+    _lib.check(lib.ngp_microbench_l2_gather(None, table_bytes, 5, C.byref(g)))
+    _lib.check(lib.ngp_microbench_l2_red(None, table_bytes, 1, 5, C.byref(r1)))
+    _lib.check(lib.ngp_microbench_l2_red(None, table_bytes, 2, 5, C.byref(r2)))
+    enc = cfg["encoding"]; corners = enc["n_levels"] * 8
+    sm_hz = (clocks.get("sm_mhz") or 1965.0) * 1e6
+    issue_peak = 148 * 4 * sm_hz            # one warp instruction per cycle per SM sub-partition
     kernels = {}
     nested = {"train_nerf_step", "density_grid_update"}      # enclosing scopes, not kernels
     for name, r in prof.items():
         if name in nested or r["count"] == 0:
             continue
         a = algorithmic(name, cfg)
-        row = {"launches_per_step": r["count"] / args.steps, "ms_per_step": r["ms"] / args.steps, "avg_ms": r["ms"] / r["count"], "units_per_launch": r["units"] / r["count"]}
+        t_launch = r["ms"] / r["count"] * 1e-3
+        units = r["units"] / r["count"]
+        row = {"launches_per_step": r["count"] / prof_steps, "ms_per_step": r["ms"] / prof_steps, "avg_ms": r["ms"] / r["count"], "units_per_launch": units}
         if a and a[1]:
-            per_launch = a[1] * r["units"] / r["count"]
-            ach = per_launch / (r["ms"] / r["count"] * 1e-3)
+            ach = a[1] * units / t_launch
             if a[0] == "hbm":
                 row.update(bound="hbm", achieved=ach / 1e9, peak=peaks["hbm_gbs"], unit="GB/s", frac=ach / 1e9 / peaks["hbm_gbs"], per_unit=a[1])
             else:
                 row.update(bound="tensor", achieved=ach / 1e12, peak=peaks["tflops_sustained"], unit="TFLOP/s", frac=ach / 1e12 / peaks["tflops_sustained"], per_unit=a[1])
             row["traffic"] = traffic.get(name)
+        elif name in inst:
+            # issue-bound kernels (the marcher, the compositor): warp instructions per unit from the committed ncu capture
+            # (profiles/instructions.json: smsp__inst_executed.sum / units of that launch) x this launch's units / its time,
+            # against one warp instruction per cycle per SM sub-partition at the SM clock sampled during the timed windows
+            per_unit = inst[name]["warp_inst_per_unit"]
+            ach = per_unit * units / t_launch
+            row.update(bound="issue", achieved=ach / 1e9, peak=issue_peak / 1e9, unit="Gwarp-inst/s", frac=ach / issue_peak, per_unit=per_unit, traffic=traffic.get(name))
+        if name == "grid_forward":      # the metric's own roofline: fraction of the measured random-gather rate of this GPU's L2 / HBM
+            gathers = corners * units / t_launch
+            row["l2_gather"] = {"achieved_Ggathers_per_s": gathers / 1e9, "peak_Ggathers_per_s": g.value / 1e9, "frac": gathers / g.value,
+                                "peak_how": f"ngp_microbench_l2_gather over {table_bytes} B (table size), 32 independent 4-byte loads in flight per thread"}
+            row["gpoints_per_s"] = units / t_launch / 1e9
+        if name == "grid_backward":     # scattered fp16x2 reductions: 8 corners x L entries per point; best case = every x-neighbour pair in one lane
+            ent = corners * units / t_launch
+            peak_ent = max(r1.value, 2.0 * r2.value)
+            row["l2_red"] = {"achieved_Gentries_per_s": ent / 1e9, "peak_Gentries_per_s": peak_ent / 1e9, "frac": ent / peak_ent,
+                             "red_f16x2_Glanes_per_s": r1.value / 1e9, "red_v2_f16x2_Glanes_per_s": r2.value / 1e9,
+                             "peak_how": "max(ngp_microbench_l2_red vec 1, 2 x vec 2): scattered red.global.add lanes/s over a table-sized buffer; "
+                                         "2 entries per lane = both x-neighbour corners merged, the most this access pattern allows"}
+            row["gpoints_per_s"] = units / t_launch / 1e9
         kernels[name] = row
     step_ms_prof = sum(k["ms_per_step"] for k in kernels.values())
     cand = [k for k in kernels if "achieved" in kernels[k]]
-    top = max(cand, key=lambda k: kernels[k]["ms_per_step"])
+    top = max(cand, key=lambda k: kernels[k]["ms_per_step"])      # the kernel group with the largest time that has a model (all main ones do)
     roof = {k: kernels[top][k] for k in ("bound", "achieved", "peak", "unit", "frac", "traffic")}
+    src = {"tensor": ", sustained bf16", "hbm": ", copy bandwidth", "issue": f": 148 SMs x 4 schedulers x {sm_hz / 1e6:.0f} MHz sampled under load"}[roof["bound"]]
     roof.update(kernel=top, share_of_step=kernels[top]["ms_per_step"] / step_ms_prof, avg_ms=kernels[top]["avg_ms"],
-                peak_source=peaks["source"] + (", sustained bf16" if roof["bound"] == "tensor" else ", copy bandwidth"))
+                peak_source=(peaks["source"] if roof["bound"] != "issue" else "issue rate") + src)
+    for extra in ("l2_gather", "l2_red"):
+        if extra in kernels[top]:
+            roof[extra] = kernels[top][extra]
 
+    rate = lambda r: r[1] / (r[0] * 1e-3)
     line = {"metric": METRIC, "value": n_samples / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16 (fp32 accumulate, fp32 master weights)",
             "data": "synthetic",
             "config": {"workload": workload_name(args), "global_batch": batch * world, "per_gpu_batch": batch, "parallelism": f"dp{world}" if world > 1 else "single",
                        "pretrain_steps_untimed": args.pretrain, "samples_before_compaction_per_step": n_before / args.steps / world,
                        "rays_per_batch": tb.stats.rays_per_batch, "n_params": int(tb.n_params()), "steps_with_prefetched_rays": prefetch_hits,
-                       "l2_policy": "inputs larger than L2: 256 MB image set + 24 MB table + >100 MB sample buffers touched every step"},
+                       "l2_policy": "inputs larger than L2: 256 MB image set + 24 MB table + >100 MB sample buffers touched every step",
+                       "l2_persisting_window_bytes": int(tb.get_option("l2_window_bytes"))},
+            "windows": {"repeats": len(rows), "steps_each": args.steps, "value_median": rate(rows[len(rows) // 2]), "value_min": rate(rows[0]), "value_max": rate(rows[-1]),
+                        "ms_per_step_min": min(r[0] for r in rows) / args.steps, "ms_per_step_max": max(r[0] for r in rows) / args.steps},
             "e2e": {"value": n_e2e / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": view_bytes, "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / args.steps,
-                    "api": "pyngp.Testbed.set_training_image + train + loss"},
+                    "api": "pyngp.Testbed.set_training_image + train + loss", "repeats": len(rows_e2e), "value_min": rate(rows_e2e[0]), "value_max": rate(rows_e2e[-1])},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "kernels": kernels}
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        r = cpu_arm(8, 1, 1 << 12, 8, 200, args.log2_hashmap_size)
+        state = trained_state(tb)
+        r = cpu_arm(args, views, state, max(1, args.cpu_steps - 1), 1, batch, f"the own arm's parameters / occupancy grid after {int(tb.stats.training_step)} steps, read back to the host")
         line["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
     if rank == 0:
         print(json.dumps(line), flush=True)
@@ -341,6 +453,8 @@ def main():
     ap.add_argument("--batch", type=int, default=BATCH)
     ap.add_argument("--log2-hashmap-size", type=int, default=19)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--repeats", type=int, default=15, help="K-step windows timed back to back; the median is reported")
+    ap.add_argument("--cpu-steps", type=int, default=3, help="timed steps of the CPU arm (a full-batch step takes seconds)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -202,9 +202,11 @@ int ngp_testbed_pending_counters(ngp_testbed_t t, uint32_t* measured_batch_size,
 int ngp_testbed_set_shard(ngp_testbed_t t, uint32_t rank, uint32_t world_size);
 /* Data-parallel step inside the library (ngp_comm_init / ngp_allreduce_gradients).  Rank 0 obtains an NCCL unique id
  * (128 bytes), the host distributes it, every rank calls ngp_testbed_comm_init (collective).  From then on ngp_testbed_train
- * shards the rays by rank, all-reduces the two sample counters under the backward pass and the fp16 gradient vector
- * (layout nerf_network.h:430-443) slice by slice — MLP weights, then one hash-level chunk at a time — on a communication
- * stream beside the remaining backward kernels; every rank then runs the identical optimizer step.  NCCL is bound at run
+ * shards the rays by rank, all-reduces the two sample counters under the backward pass and then the whole fp16 gradient vector
+ * (layout nerf_network.h:430-443) in ONE collective behind the backward pass on a communication stream (cutting it into
+ * hash-level slices that overlap the scatter was measured slower at this message size; NGP_DP_SLICES
+ * re-enables it for experiments); every rank then runs the identical optimizer step — or, with "dp_sharded_optimizer" = 1,
+ * reduce-scatter -> Adam on this rank's 1/world of the entries -> all-gather of the fp16 parameters.  NCCL is bound at run
  * time: nccl_lib_path names libnccl.so.2 (NULL: the copy already loaded in the process, $NGP_NCCL_LIB, or the system one). */
 int ngp_comm_unique_id(void* out_128_bytes, const char* nccl_lib_path);
 int ngp_testbed_comm_init(ngp_testbed_t t, const void* id_128_bytes, uint32_t rank, uint32_t world_size, const char* nccl_lib_path);
@@ -241,7 +243,9 @@ int ngp_testbed_training_view(ngp_testbed_t t, uint32_t i, ngp_training_image* o
 uint32_t ngp_testbed_n_training_views(ngp_testbed_t t);
 int ngp_testbed_compute_image_mse(ngp_testbed_t t, void* stream, int32_t quantize_to_byte, float* mse_out);   /* python_api.cu:444 */
 /* runtime knobs (pyngp def_readwrite members, python_api.cu:452-537,611-695); value semantics per name:
- * "random_bg_color","linear_colors","snap_to_pixel_centers","shall_train_encoding","shall_train_network" (bool),
+ * "random_bg_color","linear_colors","shall_train_encoding","shall_train_network" (bool),
+ * "train_snap_to_pixel_centers" (bool, default 1: nerf.training.snap_to_pixel_centers, training rays),
+ * "snap_to_pixel_centers" (bool, default 0: Testbed::m_snap_to_pixel_centers, render rays: pixel offset of sample 0 for every sample),
  * "near_distance","density_grid_decay","render_min_transmittance","cone_angle_constant" (float),
  * "loss_type","rgb_activation","density_activation" (enum), "seed" (integer), "image_snap_to_pixel_centers",
  * "image_linear_colors","image_stratified" (bool), "background_r/g/b" (float),

@@ -406,7 +406,7 @@ int ngp_testbed_debug_buffer(ngp_testbed_t t, const char* name, void** ptr, uint
 }
 
 #define NGP_OPTIONS(X)                                                                                                           \
-    X(random_bg_color, bool) X(linear_colors, bool) X(snap_to_pixel_centers, bool) X(shall_train_encoding, bool) X(shall_train_network, bool) \
+    X(random_bg_color, bool) X(linear_colors, bool) X(snap_to_pixel_centers, bool) X(train_snap_to_pixel_centers, bool) X(shall_train_encoding, bool) X(shall_train_network, bool) \
     X(near_distance, float) X(density_grid_decay, float) X(render_min_transmittance, float) X(cone_angle_constant, float)         \
     X(loss_type, int) X(rgb_activation, int) X(density_activation, int) X(seed, uint64_t)                                        \
     X(image_snap_to_pixel_centers, bool) X(image_linear_colors, bool) X(image_stratified, bool) X(sampler_lanes_per_ray, uint32_t) X(prefetch_rays, bool) X(prefetch_hits, uint32_t)
@@ -432,6 +432,7 @@ int ngp_testbed_get_option(ngp_testbed_t t, const char* name, double* value) {
     if (n == "background_r") { *value = t->tb.background_color[0]; return 0; }
     if (n == "background_g") { *value = t->tb.background_color[1]; return 0; }
     if (n == "background_b") { *value = t->tb.background_color[2]; return 0; }
+    if (n == "l2_window_bytes") { *value = t->tb.trainer() ? (double)t->tb.trainer()->l2_window_bytes : 0.0; return 0; }   // read-only
     throw Error("unknown option '" + n + "'");
     NGP_API_END
 }

@@ -71,7 +71,7 @@ static Json lens_json(const ImageMeta& m) {   // to_json(Lens) (json_binding.h:1
 }
 
 // to_json(NerfDataset) (json_binding.h:224-251): poses and intrinsics of the training views, no pixels
-static Json dataset_json(const std::vector<ImageMeta>& metas, const Aabb& render_aabb, int aabb_scale, bool is_hdr) {
+static Json dataset_json(const std::vector<ImageMeta>& metas, const Aabb& render_aabb, int aabb_scale, bool is_hdr, float scale, const float* offset) {
     Json j; j.type = Json::Object;
     j["n_images"] = Json::integer((int64_t)metas.size());
     Json paths, md, xf; paths.type = md.type = xf.type = Json::Array;
@@ -91,13 +91,13 @@ static Json dataset_json(const std::vector<ImageMeta>& metas, const Aabb& render
     }
     j["paths"] = paths; j["metadata"] = md; j["xforms"] = xf;
     j["render_aabb"] = aabb_json(render_aabb);
-    const float eye[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}, up[3] = {0, 1, 0}, off[3] = {0.5f, 0.5f, 0.5f};
+    const float eye[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}, up[3] = {0, 1, 0};
     Json r2l; r2l.type = Json::Array; for (int r = 0; r < 3; ++r) r2l.arr.push_back(vec_json(eye + 3 * r, 3));
     j["render_aabb_to_local"] = r2l;
-    j["up"] = vec_json(up, 3); j["offset"] = vec_json(off, 3);             // NerfDataset defaults (nerf_loader.h:120-140)
+    j["up"] = vec_json(up, 3); j["offset"] = vec_json(offset, 3);          // the loaded dataset's scale / offset (nerf_loader.cu:388-393); up: loader default
     Json er; er.type = Json::Array; er.arr.push_back(Json::integer(0)); er.arr.push_back(Json::integer(0));
     j["envmap_resolution"] = er;
-    j["scale"] = Json::number(0.33f);
+    j["scale"] = Json::number(scale);
     j["aabb_scale"] = Json::integer(aabb_scale);
     j["from_mitsuba"] = Json::boolean(false);
     j["is_hdr"] = Json::boolean(is_hdr);
@@ -153,7 +153,7 @@ void Testbed::save_snapshot(cudaStream_t s, const std::string& path, bool includ
         rgb["measured_batch_size"] = Json::integer(m_measured);
         rgb["measured_batch_size_before_compaction"] = Json::integer(m_measured_before);
         nerf["rgb"] = rgb;
-        nerf["dataset"] = dataset_json(m_host_metas, render_aabb, m_aabb_scale, !m_all_images_u8);
+        nerf["dataset"] = dataset_json(m_host_metas, render_aabb, m_aabb_scale, !m_all_images_u8, m_ds_scale, m_ds_offset);
         snap["nerf"] = nerf;
     }
     snap["training_step"] = Json::integer(m_training_step);
@@ -254,6 +254,8 @@ void Testbed::load_snapshot(cudaStream_t s, const std::string& path) {
                 mat4x3_from_json(d.at("xforms").arr.at(i).at("start"), m.xform);
             }
             aabb_scale = (int)d.value("aabb_scale", (double)aabb_scale);
+            m_ds_scale = (float)d.value("scale", (double)m_ds_scale);
+            if (d.contains("offset") && d.at("offset").arr.size() == 3) for (int k = 0; k < 3; ++k) m_ds_offset[k] = (float)d.at("offset").arr[k].num;
         }
         load_nerf_post(s, aabb_scale);
         m_rays_per_batch = (uint32_t)nerf.at("rgb").at("rays_per_batch").num;

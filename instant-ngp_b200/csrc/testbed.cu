@@ -21,6 +21,16 @@ static int loss_type_from_string(const std::string& s) {   // string_to_loss_typ
     throw Error("Unknown loss type '" + s + "'");
 }
 
+// RGBA8 pixels equal to 0x00FF00FF are "masked away" (read_rgba, common_device.cuh:885-913): the training walk skips rays that
+// land on them, i.e. the walk depends on the image CONTENT only through this one value.  One pass over the host buffer
+// (auto-vectorised OR-reduction, ~0.1 ms for an 800x800 view) tells whether a view has any.
+static bool has_mask_pixels(const void* pixels, size_t n_pixels) {
+    const uint32_t* p = static_cast<const uint32_t*>(pixels);
+    uint32_t any = 0;
+    for (size_t i = 0; i < n_pixels; ++i) any |= (uint32_t)(p[i] == 0x00FF00FFu);
+    return any != 0;
+}
+
 Testbed::Testbed(int mode) : m_mode(mode), m_rng(1337), m_density_grid_rng(1337) {
     NGP_CHECK(mode == MODE_TB_NERF || mode == MODE_TB_IMAGE || mode == MODE_TB_SDF, "Testbed: unknown mode (Nerf = 0, Sdf = 1, Image = 2)");
 }
@@ -86,6 +96,7 @@ void Testbed::set_nerf_dataset(cudaStream_t s, uint32_t n_images, const HostImag
     m_prefetch_valid = false; ++m_dataset_version; m_all_images_u8 = true;
     for (void* p : m_image_buffers) cudaFree(p);
     m_image_buffers.clear(); m_image_bytes.clear();
+    m_frame_has_mask.assign(n_images, false);
     std::vector<ImageMeta> metas(n_images);
     for (uint32_t i = 0; i < n_images; ++i) {
         const HostImage& h = images[i];
@@ -93,6 +104,7 @@ void Testbed::set_nerf_dataset(cudaStream_t s, uint32_t n_images, const HostImag
         NGP_CHECK(h.lens_mode == LENS_PERSPECTIVE || h.lens_mode == LENS_OPENCV, "lens mode must be Perspective (0) or OpenCV (1)");
         const size_t bytes = (size_t)h.res[0] * h.res[1] * (h.data_type == IMG_BYTE ? 4 : 16);
         m_all_images_u8 = m_all_images_u8 && h.data_type == IMG_BYTE;
+        if (h.data_type == IMG_BYTE) m_frame_has_mask[i] = has_mask_pixels(h.pixels, (size_t)h.res[0] * h.res[1]);
         void* d = nullptr;
         NGP_CUDA_CHECK(cudaMalloc(&d, bytes));
         m_image_buffers.push_back(d); m_image_bytes.push_back(bytes);
@@ -178,7 +190,16 @@ void Testbed::set_training_image(cudaStream_t s, uint32_t frame_idx, const void*
     NGP_CHECK(m_mode == MODE_TB_NERF, "set_training_image: testbed is not in Nerf mode");
     NGP_CHECK(frame_idx < m_n_images, "Invalid frame index");   // python_api.cu:50-52
     NGP_CHECK(pixels_host, "set_training_image: null pixels");
-    if (!m_all_images_u8) { ++m_dataset_version; if (m_aux_stream) NGP_CUDA_CHECK(cudaStreamSynchronize(m_aux_stream)); }   // RGBA8 has no masked (negative) pixels: the walk never depends on its content
+    // A prefetched walk of the next step's rays may be in flight / waiting to be adopted.  It read the OLD pixels, and only to test
+    // them against the mask colour: when neither the old nor the new RGBA8 view contains a masked pixel the walk does not depend
+    // on the content and stays valid; otherwise (and for float images, where any negative value masks) it is discarded.
+    bool content_matters = !m_all_images_u8;
+    if (m_all_images_u8) {
+        const bool new_mask = has_mask_pixels(pixels_host, m_image_bytes[frame_idx] / 4);
+        content_matters = new_mask || m_frame_has_mask[frame_idx];
+        m_frame_has_mask[frame_idx] = new_mask;
+    }
+    if (content_matters) { ++m_dataset_version; m_prefetch_valid = false; if (m_aux_stream) NGP_CUDA_CHECK(cudaStreamSynchronize(m_aux_stream)); }
     if (!m_all_images_u8) { NGP_CUDA_CHECK(cudaMemcpyAsync(m_image_buffers[frame_idx], pixels_host, m_image_bytes[frame_idx], cudaMemcpyHostToDevice, s)); return; }
     if (!m_copy_stream) {
         NGP_CUDA_CHECK(cudaStreamCreateWithFlags(&m_copy_stream, cudaStreamNonBlocking));
@@ -300,6 +321,7 @@ void Testbed::train_end(cudaStream_t s, uint32_t measured_override, uint32_t mea
     if (m_get_loss) {
         reduce_sum_f32(s, m_loss.as<float>(), m_rays_per_batch, m_loss_sum.as<float>(), m_partials.as<float>());
         NGP_CUDA_CHECK(cudaMemcpyAsync(m_host_counters + 4, m_loss_sum.as<float>(), 4, cudaMemcpyDeviceToHost, s));
+        NGP_CUDA_CHECK(cudaMemcpyAsync(m_host_counters + 7, m_mean.as<float>(), 4, cudaMemcpyDeviceToHost, s));   // stats().density_grid_mean
     }
     NGP_CUDA_CHECK(cudaEventSynchronize(m_ev_counters));
     const uint32_t* c = m_host_counters;
@@ -324,6 +346,10 @@ void Testbed::train_end(cudaStream_t s, uint32_t measured_override, uint32_t mea
     if (m_get_loss) {
         NGP_CUDA_CHECK(cudaStreamSynchronize(s));
         float loss_sum; memcpy(&loss_sum, m_host_counters + 4, 4); m_loss_scalar = loss_sum * (float)m_measured / (float)target;
+        // data parallel: every ray's loss is divided by the GLOBAL ray count but only this rank's rays are summed here, so the sum is
+        // ~1/world of the step's loss; scaled back it is this rank's estimate of the global mean (comparable with single-GPU runs)
+        m_loss_scalar *= (float)m_world;
+        memcpy(&m_density_grid_mean, m_host_counters + 7, 4);
     }
 }
 
@@ -332,7 +358,7 @@ TrainStats Testbed::stats() const {
     st.training_step = m_training_step; st.loss = m_loss_scalar; st.rays_per_batch = m_rays_per_batch; st.measured_batch_size = m_measured;
     st.measured_batch_size_before_compaction = m_measured_before; st.n_rays_total = m_n_rays_total;
     st.learning_rate = m_trainer ? m_trainer->opt.current_lr : 0.f;
-    st.density_grid_mean = 0.f;
+    st.density_grid_mean = m_density_grid_mean;
     return st;
 }
 
@@ -342,7 +368,7 @@ TrainStats Testbed::stats() const {
 // ---------------------------------------------------------------------------------------------------------------
 Testbed::SamplerKey Testbed::sampler_key(uint32_t n_rays, uint32_t max_inference, uint32_t target) const {
     return {m_training_step, n_rays, max_inference, target, m_rank, m_world, sampler_lanes_per_ray, m_dataset_version, m_rng.state, m_rng.inc,
-            cone_angle_constant, snap_to_pixel_centers};
+            cone_angle_constant, train_snap_to_pixel_centers};
 }
 
 SamplerBuffers Testbed::sampler_buffers(cudaStream_t s, uint32_t set, uint32_t target, uint32_t n_rays) {
@@ -380,7 +406,7 @@ uint32_t Testbed::max_inference_samples(uint32_t target) {
 void Testbed::launch_sampler(cudaStream_t s, const SamplerKey& key, const SamplerBuffers& sb) {
     NGP_CUDA_CHECK(cudaMemsetAsync(sb.counters, 0, 32, s));
     nerf_generate_training_samples(s, key.n_rays, aabb, key.max_inference, 0, m_rng, m_n_images, m_metas.as<ImageMeta>(), m_bitfield.as<uint8_t>(), m_max_cascade,
-                                   snap_to_pixel_centers, cone_angle_constant, m_rank * key.n_rays, m_world * key.n_rays, sb);
+                                   train_snap_to_pixel_centers, cone_angle_constant, m_rank * key.n_rays, m_world * key.n_rays, sb);
 }
 
 // The rays of step N + 1 depend on the rng, the control law's rays_per_batch (known once step N's loss has run) and the
@@ -448,7 +474,7 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
 
     LossConfig lc{};
     lc.loss_type = loss_type; lc.rgb_activation = rgb_activation; lc.density_activation = density_activation;
-    lc.random_bg_color = random_bg_color; lc.linear_colors = linear_colors; lc.snap_to_pixel_centers = snap_to_pixel_centers;
+    lc.random_bg_color = random_bg_color; lc.linear_colors = linear_colors; lc.snap_to_pixel_centers = train_snap_to_pixel_centers;
     memcpy(lc.background_color, background_color, sizeof(lc.background_color));
     lc.loss_scale = LOSS_SCALE; lc.near_distance = near_distance;
     lb.enc_in = m_nerf_net->last_inference_encoding();   // written by inference() just above
@@ -587,7 +613,7 @@ void Testbed::render(cudaStream_t s, const float* camera_matrix, const float* fo
     cam.lens_mode = render_lens_mode; memcpy(cam.lens_params, render_lens_params, 16);
     NGP_CUDA_CHECK(cudaMemsetAsync(accum, 0, (size_t)n_pixels * 16, s));
     for (int sample = 0; sample < spp; ++sample) {
-        nerf_init_rays(s, cam, (uint32_t)sample, snap_to_pixel_centers && spp == 1, render_aabb, m_bitfield.as<uint8_t>(), m_max_cascade, cone_angle_constant, rays[0], frame, fdepth);
+        nerf_init_rays(s, cam, (uint32_t)sample, snap_to_pixel_centers, render_aabb, m_bitfield.as<uint8_t>(), m_max_cascade, cone_angle_constant, rays[0], frame, fdepth);
         NGP_CUDA_CHECK(cudaMemsetAsync(counters, 0, 16, s));
         uint32_t n_alive = n_pixels, i = 1, db = 0;
         while (i < MARCH_ITER) {

@@ -86,7 +86,10 @@ public:
     void debug_buffer(const std::string& name, void** ptr, uint64_t* bytes);
 
     // runtime knobs (pyngp def_readwrite members: python_api.cu:452-537,611-695)
-    bool random_bg_color = true, linear_colors = false, snap_to_pixel_centers = true, shall_train_encoding = true, shall_train_network = true;
+    bool random_bg_color = true, linear_colors = false, shall_train_encoding = true, shall_train_network = true;
+    // two different members of the reference: nerf.training.snap_to_pixel_centers (training rays, default true, testbed.h:773) and
+    // Testbed::m_snap_to_pixel_centers (render rays, default false, python_api.cu:478)
+    bool train_snap_to_pixel_centers = true, snap_to_pixel_centers = false;
     float near_distance = 0.1f, density_grid_decay = 0.95f, render_min_transmittance = 0.01f, cone_angle_constant = 0.0f;
     float background_color[3] = {0.f, 0.f, 0.f};
     int loss_type = LOSS_L2, rgb_activation = ACT_LOGISTIC, density_activation = ACT_EXPONENTIAL;
@@ -133,6 +136,8 @@ private:
     uint32_t m_rank = 0, m_world = 1;
 
     // NeRF dataset + occupancy grid
+    float m_density_grid_mean = 0.f;      // host copy, refreshed with the loss every 16th step
+    std::vector<bool> m_frame_has_mask;   // RGBA8 view contains the mask colour 0x00FF00FF (see set_training_image)
     uint32_t m_n_images = 0; int m_aabb_scale = 1; uint32_t m_max_cascade = 0;
     std::vector<void*> m_image_buffers; std::vector<size_t> m_image_bytes; DeviceBuffer m_metas; std::vector<ImageMeta> m_host_metas;
     DeviceBuffer m_density_grid, m_density_grid_tmp, m_bitfield, m_mean, m_partials, m_grid_pos, m_grid_idx, m_grid_out;

@@ -52,7 +52,7 @@ def _stream():
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
-_BOOL_OPTS = {"random_bg_color", "linear_colors", "snap_to_pixel_centers", "shall_train_encoding", "shall_train_network",
+_BOOL_OPTS = {"random_bg_color", "linear_colors", "snap_to_pixel_centers", "train_snap_to_pixel_centers", "shall_train_encoding", "shall_train_network",
               "image_snap_to_pixel_centers", "image_linear_colors", "image_stratified", "prefetch_rays"}
 _FLOAT_OPTS = {"near_distance", "density_grid_decay", "render_min_transmittance", "cone_angle_constant"}
 _INT_OPTS = {"loss_type", "rgb_activation", "density_activation", "seed", "sampler_lanes_per_ray", "prefetch_hits"}
@@ -125,7 +125,7 @@ class Testbed:
         object.__setattr__(self, "_dist", None)
         training = _Namespace(self, {"random_bg_color": "random_bg_color", "loss_type": "loss_type", "near_distance": "near_distance",
                                      "density_grid_decay": "density_grid_decay", "linear_colors": "linear_colors",
-                                     "snap_to_pixel_centers": "snap_to_pixel_centers"},
+                                     "snap_to_pixel_centers": "train_snap_to_pixel_centers"},
                               {"set_image": self.set_training_image, "set_camera_intrinsics": self.set_camera_intrinsics,
                                "set_camera_extrinsics": self.set_camera_extrinsics, "dataset": _Dataset(self),
                                "n_images_for_training": _Lazy(self.n_training_views)})
@@ -165,6 +165,12 @@ class Testbed:
             check(lib().ngp_testbed_get_option(self._h, name.encode(), C.byref(v)))
             return bool(v.value) if name in _BOOL_OPTS else (float(v.value) if name in _FLOAT_OPTS else int(v.value))
         raise AttributeError(name)
+
+    def get_option(self, name):
+        """any option of ngp_testbed_get_option by name (incl. read-only diagnostics such as "l2_window_bytes")"""
+        v = C.c_double()
+        check(lib().ngp_testbed_get_option(self._h, name.encode(), C.byref(v)))
+        return v.value
 
     def __setattr__(self, name, value):
         if name in _BOOL_OPTS | _FLOAT_OPTS | _INT_OPTS:

@@ -82,6 +82,25 @@ class CpuNerfTrainer:
         self.loss = 0.0
         self.timings = {}
 
+    def adopt_state(self, st):
+        """Continue from a trained state (dict of numpy arrays / ints, e.g. read back from the CUDA Testbed): parameters, optimizer
+        moments, occupancy grid + bitfield, step counters.  bench.py uses it so that the CPU arm times the SAME steady-state step
+        as the GPU arm (sparsified occupancy grid, settled rays_per_batch) without training for minutes on the host first."""
+        self.master = np.ascontiguousarray(st["master"], np.float32); self.params = np.ascontiguousarray(st["params"], np.float16)
+        assert self.master.size == self.n_params and self.params.size == self.n_params
+        for k in ("m", "v", "ema"):
+            if k in st: setattr(self, k, np.ascontiguousarray(st[k], np.float32))
+        if "steps" in st: self.steps = np.ascontiguousarray(st["steps"], np.uint32)
+        if "ema_h" in st: self.ema_h = np.ascontiguousarray(st["ema_h"], np.float16)
+        self.grid = np.ascontiguousarray(st["density_grid"], np.float32); self.bitfield = np.ascontiguousarray(st["bitfield"], np.uint8)
+        self.mean_density = float(st["mean_density"])
+        self.training_step = int(st["training_step"]); self.opt_steps = int(st.get("opt_steps", self.training_step))
+        self.rays_per_batch = int(st["rays_per_batch"]); self.measured_before = int(st["measured_before"]); self.measured = int(st.get("measured", 0))
+        self.rng_skip = 1 + self.training_step * (1 << 32)          # m_rng.advance() once per step (testbed_nerf.cu:4127)
+        # occupancy-grid refreshes so far: every clamp(step/16, 1, 16) steps (testbed.cu:4321); two rng advances per refresh
+        n_upd = sum(1 for t in range(self.training_step) if t % min(max(t // 16, 1), 16) == 0)
+        self.dg_step = int(st.get("dg_step", n_upd)); self.dg_skip = int(st.get("dg_skip", n_upd * 2 * (1 << 32)))
+
     def _t(self, name, t0):
         self.timings[name] = self.timings.get(name, 0.0) + time.perf_counter() - t0
 

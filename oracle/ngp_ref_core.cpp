@@ -480,3 +480,8 @@ extern "C" void ref_ema_step(uint64_t n, float decay, uint32_t step, const uint1
         ema[i] = f; ema_h[i] = f2h(f);
     }
 }
+
+// ---- OpenMP control (bench.py: torchrun exports OMP_NUM_THREADS=1, which would silently cap the CPU arm) ----
+#include <omp.h>
+extern "C" void ref_set_num_threads(int n) { if (n > 0) omp_set_num_threads(n); }
+extern "C" int ref_get_max_threads() { return omp_get_max_threads(); }
