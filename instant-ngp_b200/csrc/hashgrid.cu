@@ -417,8 +417,10 @@ void grid_forward(cudaStream_t s, const GridLayout& g, const __half* table, cons
 
 // runs per warp up to which a level is aggregated (0 = never); NGP_AGG_MAX_RUNS overrides for experiments.  Measured (tools/sweep_agg.sh,
 // grid_backward ms per 2^18 samples, synthetic scene / fox): 0: 0.119 / 0.359, 4: 0.109 / 0.216, 8: 0.113 / 0.184, 12: 0.108 / 0.163, 16: 0.126 / 0.141
-static bool red_wide() {   // NGP_RED_V4=0: aligned-pair (8-byte) merging only, for A/B measurements
-    static const bool v = [] { const char* e = getenv("NGP_RED_V4"); return e ? atoi(e) != 0 : true; }();
+static bool red_wide() {   // NGP_RED_V4=1: 16-byte group merging.  Measured on B200 (profiles/r02_ab_l2_red.json): 0.086 -> 0.095 ms per 2^18 samples, i.e.
+    // SLOWER than aligned-pair merging — the scattered-RED lane rate is the same for 4 / 8 / 16-byte lanes (179 G lanes/s, ngp_microbench_l2_red)
+    // and the slot selects cost more issue slots than the 1/6 fewer lanes return.  Off by default, kept for experiments.
+    static const bool v = [] { const char* e = getenv("NGP_RED_V4"); return e ? atoi(e) != 0 : false; }();
     return v;
 }
 static uint32_t agg_max_runs() {

@@ -30,6 +30,34 @@ NGP_D void load_weights_blk8(__half* dst, const __half* __restrict__ src, uint32
     }
 }
 
+// the same with compile-time shapes: every 16-byte load of the thread is issued before the first store (the rolled loop above
+// exposes one global-load latency per iteration: ~10 x 800 cycles of prologue per CTA for the 20 KB of the NeRF networks)
+template <uint32_t ROWS, uint32_t COLS, uint32_t NT>
+NGP_D void load_weights_blk8_t(__half* dst, const __half* __restrict__ src, uint32_t tid) {
+    constexpr uint32_t CPR = COLS / 8, N = ROWS * CPR, IT = (N + NT - 1) / NT;
+    uint4 v[IT];
+#pragma unroll
+    for (uint32_t k = 0; k < IT; ++k) { const uint32_t i = tid + k * NT; if (i < N) v[k] = __ldg(reinterpret_cast<const uint4*>(src + (size_t)(i / CPR) * COLS + (i % CPR) * 8)); }
+#pragma unroll
+    for (uint32_t k = 0; k < IT; ++k) { const uint32_t i = tid + k * NT; if (i < N) *reinterpret_cast<uint4*>(dst + blk8_chunk_offset(i / CPR, i % CPR, COLS)) = v[k]; }
+}
+// all layers of the density / plain chain and (MODE_NERF) the rgb chain into their shared-memory slots
+template <uint32_t PW, uint32_t DH, uint32_t RH, bool NERF, uint32_t NT>
+NGP_D void load_all_weights(uint8_t* smem, const uint32_t* wd, const uint32_t* wr, const __half* __restrict__ w_density, const __half* __restrict__ w_rgb, uint32_t tid) {
+    const __half* w = w_density;
+    load_weights_blk8_t<MLP_WIDTH, PW, NT>(reinterpret_cast<__half*>(smem + wd[0]), w, tid); w += MLP_WIDTH * PW;
+#pragma unroll
+    for (uint32_t l = 1; l < DH; ++l) { load_weights_blk8_t<MLP_WIDTH, MLP_WIDTH, NT>(reinterpret_cast<__half*>(smem + wd[l]), w, tid); w += MLP_WIDTH * MLP_WIDTH; }
+    load_weights_blk8_t<MLP_OUT_PAD, MLP_WIDTH, NT>(reinterpret_cast<__half*>(smem + wd[DH]), w, tid);
+    if (NERF) {
+        w = w_rgb;
+        load_weights_blk8_t<MLP_WIDTH, 32, NT>(reinterpret_cast<__half*>(smem + wr[0]), w, tid); w += MLP_WIDTH * 32;
+#pragma unroll
+        for (uint32_t l = 1; l < RH; ++l) { load_weights_blk8_t<MLP_WIDTH, MLP_WIDTH, NT>(reinterpret_cast<__half*>(smem + wr[l]), w, tid); w += MLP_WIDTH * MLP_WIDTH; }
+        load_weights_blk8_t<MLP_OUT_PAD, MLP_WIDTH, NT>(reinterpret_cast<__half*>(smem + wr[RH]), w, tid);
+    }
+}
+
 NGP_D uint4 pack8(const float* v, bool relu) {
     uint32_t h[4];
 #pragma unroll
@@ -107,6 +135,7 @@ struct FwdParams {
     const float* coords;      // [n][7] (MODE_NERF)
     __half* out; uint32_t out_stride;
     uint32_t n_tiles;
+    long long* probe;         // debug (NGP_MLP_PROBE=1): per-phase clock64 deltas of CTA 0 / thread 0, summed over its tiles; null in normal runs
 };
 
 template <uint32_t PW, uint32_t DH, uint32_t RH, int MODE>
@@ -144,22 +173,7 @@ __global__ void __launch_bounds__(128) mlp_forward_kernel(const FwdParams p) {
     // ---- one-time setup: barriers, TMEM, weights ----
     if (tid == 0) { mbar_init(&bar_full[0], 1); mbar_init(&bar_full[1], 1); mbar_init(bar_mma, 1); mbar_fence_init(); }
     if (warp == 0) tmem_alloc<64>(tmem_slot);
-    {
-        uint32_t in_w = PW; const __half* w = p.w_density;
-        for (uint32_t l = 0; l <= DH; ++l) {
-            const uint32_t rows = (l == DH) ? MLP_OUT_PAD : MLP_WIDTH;
-            load_weights_blk8(reinterpret_cast<__half*>(smem + L.wd[l]), w, rows, in_w, tid, 128);
-            w += rows * in_w; in_w = MLP_WIDTH;
-        }
-        if (MODE == MODE_NERF) {
-            in_w = 32; w = p.w_rgb;
-            for (uint32_t l = 0; l <= RH; ++l) {
-                const uint32_t rows = (l == RH) ? MLP_OUT_PAD : MLP_WIDTH;
-                load_weights_blk8(reinterpret_cast<__half*>(smem + L.wr[l]), w, rows, in_w, tid, 128);
-                w += rows * in_w; in_w = MLP_WIDTH;
-            }
-        }
-    }
+    load_all_weights<PW, DH, RH, MODE == MODE_NERF, 128>(smem, L.wd, L.wr, p.w_density, p.w_rgb, tid);
     fence_proxy_async();
     fence_before_sync();
     __syncthreads();
@@ -231,6 +245,172 @@ __global__ void __launch_bounds__(128) mlp_forward_kernel(const FwdParams p) {
     fence_before_sync();
     __syncthreads();
     if (warp == 0) tmem_dealloc<64>(tmem_base);
+}
+
+
+// -----------------------------------------------------------------------------------------------------------------
+// Forward, "TS" form (round 2): hidden activations never touch shared memory.  The epilogue of a layer reads its TMEM
+// accumulator row (tcgen05.ld), applies ReLU, rounds to fp16 and writes the row straight back to TMEM (tcgen05.st) as
+// the A operand of the next layer's MMA, which is issued in the A-from-TMEM form.  Measured on B200
+// (tools/ubench_tc*.cu, profiles/r02_ubench_tc.txt): a K=16 M128xN64 instruction costs 50 cycles with A in shared memory
+// (its 4 KB A read at 128 B/cycle is the bound) and 33.6 with A in TMEM; N=16: 40.5 vs 10.6; the 128x64 epilogue is 148
+// cycles into TMEM against 322 into shared memory.  Per 128-sample tile of the NeRF network the tensor pipe is busy
+// 720 cycles in the SS form and 354 in this one.  Only the first layer (input tile delivered by TMA) reads A from smem.
+// TMEM per CTA: 64 accumulator columns + 32 operand columns (128 allocated) -> 4 CTAs per SM.
+// -----------------------------------------------------------------------------------------------------------------
+template <uint32_t PW, uint32_t DH, uint32_t RH, int MODE>
+struct FwdTsSmem {
+    uint32_t wd[DH + 1], wr[RH + 1], x0, bars, total;
+    __host__ __device__ FwdTsSmem() {
+        SmemCursor c;
+        wd[0] = c.take(MLP_WIDTH * PW * 2);
+        for (uint32_t l = 1; l < DH; ++l) wd[l] = c.take(MLP_WIDTH * MLP_WIDTH * 2);
+        wd[DH] = c.take(MLP_OUT_PAD * MLP_WIDTH * 2);
+        if (MODE == MODE_NERF) {
+            wr[0] = c.take(MLP_WIDTH * 32 * 2);
+            for (uint32_t l = 1; l < RH; ++l) wr[l] = c.take(MLP_WIDTH * MLP_WIDTH * 2);
+            wr[RH] = c.take(MLP_OUT_PAD * MLP_WIDTH * 2);
+        } else { for (uint32_t l = 0; l <= RH; ++l) wr[l] = 0; }
+        x0 = c.take(TILE_ROWS * PW * 2);
+        bars = c.take(64);
+        total = c.off + 128;
+    }
+};
+constexpr uint32_t TS_ACC = 0, TS_OPA = 64, TS_COLS = 128;   // TMEM columns: fp32 accumulator, packed-fp16 A operand, allocation
+
+// accumulator row [64 fp32] -> ReLU -> fp16 pairs -> the A-operand columns of the same lane
+NGP_D void epilogue_to_tmem64(uint32_t trow) {
+    float v[64];
+#pragma unroll
+    for (uint32_t j = 0; j < 64; j += 16) tmem_ld16(trow + TS_ACC + j, v + j);
+    tmem_wait_ld();
+    uint32_t pk[32];
+#pragma unroll
+    for (int i = 0; i < 32; ++i) asm("cvt.rn.relu.f16x2.f32 %0, %1, %2;" : "=r"(pk[i]) : "f"(v[2 * i + 1]), "f"(v[2 * i]));
+    tmem_st32(trow + TS_OPA, pk);
+    tmem_wait_st();
+}
+
+// One MMA stage of the TS kernels: every thread's TMEM stores / loads are complete (wait::st / wait::ld done by the caller),
+// sync the CTA, thread 0 issues and commits, everyone waits for the MMAs.
+struct StageTs {
+    uint64_t* bar; uint32_t parity;
+    template <class F>
+    NGP_D void run(F&& issue) {
+        fence_before_sync();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            fence_after_sync();
+            issue();
+            umma_commit(bar);
+        }
+        mbar_wait(bar, parity);
+        parity ^= 1u;
+        fence_after_sync();
+    }
+};
+
+template <uint32_t PW, uint32_t DH, uint32_t RH, int MODE>
+__global__ void __launch_bounds__(128) mlp_forward_ts_kernel(const FwdParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);
+    const FwdTsSmem<PW, DH, RH, MODE> L;
+    const uint32_t tid = threadIdx.x, warp = tid >> 5;
+    uint64_t* bar_full = reinterpret_cast<uint64_t*>(smem + L.bars);
+    uint64_t* bar_mma = bar_full + 1;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_full + 2);
+
+    if (tid == 0) { mbar_init(bar_full, 1); mbar_init(bar_mma, 1); mbar_fence_init(); }
+    if (warp == 0) tmem_alloc<TS_COLS>(tmem_slot);
+    load_all_weights<PW, DH, RH, MODE == MODE_NERF, 128>(smem, L.wd, L.wr, p.w_density, p.w_rgb, tid);
+    fence_proxy_async();
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t trow = tmem_base + ((warp * 32u) << 16);   // this warp's lane quadrant, column 0
+    const uint32_t acc = tmem_base + TS_ACC, opa = tmem_base + TS_OPA;
+    const uint32_t sbase = smem_u32(smem);
+    const Operand X0 = {sbase + L.x0, PW};
+    constexpr uint32_t X_BYTES = TILE_ROWS * PW * 2;
+
+    StageTs stage{bar_mma, 0};
+    uint32_t full_parity = 0;
+    if (tid == 0 && blockIdx.x < p.n_tiles) {
+        mbar_expect_tx(bar_full, X_BYTES);
+        bulk_g2s(smem + L.x0, p.enc + (size_t)blockIdx.x * TILE_ROWS * PW, X_BYTES, bar_full);
+    }
+    const bool probing = p.probe != nullptr && blockIdx.x == 0 && tid == 0;
+    long long tp = 0; uint32_t ph = 0;
+#define PROBE() do { if (probing) { const long long now = clock64(); p.probe[ph++] += now - tp; tp = now; } } while (0)
+    for (uint32_t tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+        if (probing) { tp = clock64(); ph = 0; p.probe[15] += 1; }
+        const uint32_t next = tile + gridDim.x;
+        const uint32_t row_g = tile * TILE_ROWS + tid;
+        uint4 sh_lo = make_uint4(0, 0, 0, 0), sh_hi = sh_lo;   // SH4 of the direction, evaluated while the input tile is still in flight
+        if (MODE == MODE_NERF) {
+            const float* c = p.coords + (size_t)row_g * 7 + 4;
+            float sh[16]; sh4(__ldg(c), __ldg(c + 1), __ldg(c + 2), sh);
+            sh_lo = pack8(sh, false); sh_hi = pack8(sh + 8, false);
+        }
+        mbar_wait(bar_full, full_parity); full_parity ^= 1u;
+        PROBE();   // 0: wait for the input tile
+
+        // ---- density / plain network: first layer reads the TMA-delivered input tile from shared memory ----
+        stage.run([&] { gemm_act_wT<64>(acc, X0, 0, Operand{sbase + L.wd[0], PW}, PW); });
+        if (tid == 0 && next < p.n_tiles) {   // the input tile is free: fetch the next one under the remaining layers
+            mbar_expect_tx(bar_full, X_BYTES);
+            bulk_g2s(smem + L.x0, p.enc + (size_t)next * TILE_ROWS * PW, X_BYTES, bar_full);
+        }
+        PROBE();   // 1: layer-0 stage
+        epilogue_to_tmem64(trow);
+        PROBE();   // 2: epilogue
+        for (uint32_t l = 1; l < DH; ++l) {
+            stage.run([&] { gemm_tmem_wT<64>(acc, opa, Operand{sbase + L.wd[l], MLP_WIDTH}, MLP_WIDTH); });
+            epilogue_to_tmem64(trow);
+        }
+        stage.run([&] { gemm_tmem_wT<16>(acc, opa, Operand{sbase + L.wd[DH], MLP_WIDTH}, MLP_WIDTH); });
+        float dout[16];
+        tmem_ld16(trow + TS_ACC, dout); tmem_wait_ld();
+        PROBE();   // 3: density output stage + ld
+        if (MODE == MODE_DENSITY) { p.out[row_g] = __float2half_rn(dout[0]); continue; }
+        if (MODE == MODE_PLAIN) {
+            uint4* o = reinterpret_cast<uint4*>(p.out + (size_t)row_g * p.out_stride);
+            o[0] = pack8(dout, false); o[1] = pack8(dout + 8, false);
+            continue;
+        }
+        // ---- rgb network: input row = [density out (16) | SH4(dir) (16)] as 16 packed columns ----
+        const __half sigma = __float2half_rn(dout[0]);
+        {
+            uint32_t pk[16];
+            const uint4 a0 = pack8(dout, false), a1 = pack8(dout + 8, false), a2 = sh_lo, a3 = sh_hi;
+            pk[0] = a0.x; pk[1] = a0.y; pk[2] = a0.z; pk[3] = a0.w; pk[4] = a1.x; pk[5] = a1.y; pk[6] = a1.z; pk[7] = a1.w;
+            pk[8] = a2.x; pk[9] = a2.y; pk[10] = a2.z; pk[11] = a2.w; pk[12] = a3.x; pk[13] = a3.y; pk[14] = a3.z; pk[15] = a3.w;
+            tmem_st16(trow + TS_OPA, pk);
+            tmem_wait_st();
+        }
+        PROBE();   // 4: SH + rgb input row
+        stage.run([&] { gemm_tmem_wT<64>(acc, opa, Operand{sbase + L.wr[0], 32}, 32); });
+        PROBE();   // 5: rgb layer-0 stage
+        epilogue_to_tmem64(trow);
+        PROBE();   // 6: epilogue
+        for (uint32_t l = 1; l < RH; ++l) {
+            stage.run([&] { gemm_tmem_wT<64>(acc, opa, Operand{sbase + L.wr[l], MLP_WIDTH}, MLP_WIDTH); });
+            epilogue_to_tmem64(trow);
+        }
+        PROBE();   // 7: rgb hidden stages + epilogues
+        stage.run([&] { gemm_tmem_wT<16>(acc, opa, Operand{sbase + L.wr[RH], MLP_WIDTH}, MLP_WIDTH); });
+        float rgb[16];
+        tmem_ld16(trow + TS_ACC, rgb); tmem_wait_ld();
+        PROBE();   // 8: rgb output stage + ld
+        __half2 o2[2] = {__floats2half2_rn(rgb[0], rgb[1]), __halves2half2(__float2half_rn(rgb[2]), sigma)};
+        *reinterpret_cast<uint2*>(p.out + (size_t)row_g * 4) = *reinterpret_cast<uint2*>(o2);
+        PROBE();   // 9: output store
+    }
+#undef PROBE
+    fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc<TS_COLS>(tmem_base);
 }
 
 
@@ -367,22 +547,7 @@ __global__ void __launch_bounds__(128) mlp_backward_kernel(const BwdParams p) {
 
     if (tid == 0) { mbar_init(bar_full, 1); mbar_init(bar_mma, 1); mbar_fence_init(); }
     if (warp == 0) tmem_alloc<Cfg::TMEM_COLS>(tmem_slot);
-    {
-        uint32_t in_w = PW; const __half* w = p.w_density;
-        for (uint32_t l = 0; l <= DH; ++l) {
-            const uint32_t rows = (l == DH) ? MLP_OUT_PAD : MLP_WIDTH;
-            load_weights_blk8(reinterpret_cast<__half*>(smem + L.wd[l]), w, rows, in_w, tid, 128);
-            w += rows * in_w; in_w = MLP_WIDTH;
-        }
-        if (MODE == MODE_NERF) {
-            in_w = 32; w = p.w_rgb;
-            for (uint32_t l = 0; l <= RH; ++l) {
-                const uint32_t rows = (l == RH) ? MLP_OUT_PAD : MLP_WIDTH;
-                load_weights_blk8(reinterpret_cast<__half*>(smem + L.wr[l]), w, rows, in_w, tid, 128);
-                w += rows * in_w; in_w = MLP_WIDTH;
-            }
-        }
-    }
+    load_all_weights<PW, DH, RH, MODE == MODE_NERF, 128>(smem, L.wd, L.wr, p.w_density, p.w_rgb, tid);
     fence_proxy_async();
     fence_before_sync();
     __syncthreads();
@@ -513,8 +678,34 @@ static uint32_t persistent_grid(K kernel, uint32_t smem_bytes, uint32_t tmem_col
     return std::min<uint32_t>(n_tiles, per_sm * (uint32_t)sm_count());
 }
 
+static bool mlp_ts_form() {   // NGP_MLP_TS=0: the round-1 kernels (every operand in shared memory), for A/B measurements
+    static const bool v = [] { const char* e = getenv("NGP_MLP_TS"); return e ? atoi(e) != 0 : true; }();
+    return v;
+}
+
 template <uint32_t PW, uint32_t DH, uint32_t RH, int MODE>
 static void launch_fwd(cudaStream_t s, const FwdParams& p) {
+    if (mlp_ts_form()) {
+        const FwdTsSmem<PW, DH, RH, MODE> L;
+        auto k = mlp_forward_ts_kernel<PW, DH, RH, MODE>;
+        const uint32_t grid = persistent_grid(k, L.total, TS_COLS, p.n_tiles);
+        static const bool probe = getenv("NGP_MLP_PROBE") != nullptr;
+        if (probe && MODE == MODE_NERF && p.n_tiles > 1024) {   // debug: phase breakdown of one CTA, printed to stderr
+            FwdParams q = p; long long* d = nullptr; long long h[16];
+            NGP_CUDA_CHECK(cudaMalloc(&d, sizeof(h))); NGP_CUDA_CHECK(cudaMemsetAsync(d, 0, sizeof(h), s));
+            q.probe = d;
+            k<<<grid, 128, L.total, s>>>(q);
+            NGP_POST_LAUNCH();
+            NGP_CUDA_CHECK(cudaMemcpyAsync(h, d, sizeof(h), cudaMemcpyDeviceToHost, s)); NGP_CUDA_CHECK(cudaStreamSynchronize(s)); cudaFree(d);
+            fprintf(stderr, "[ngp] mlp_forward_ts probe: %lld tiles of CTA 0 (grid %u, %u tiles), cycles per tile by phase:", h[15], grid, p.n_tiles);
+            for (int i = 0; i < 10; ++i) fprintf(stderr, " %lld", h[15] ? h[i] / h[15] : 0);
+            fprintf(stderr, "\n");
+            return;
+        }
+        k<<<grid, 128, L.total, s>>>(p);
+        NGP_POST_LAUNCH();
+        return;
+    }
     const FwdSmem<PW, DH, RH, MODE> L;
     auto k = mlp_forward_kernel<PW, DH, RH, MODE>;
     const uint32_t grid = persistent_grid(k, L.total, 64, p.n_tiles);
@@ -573,14 +764,14 @@ void nerf_mlp_forward(cudaStream_t s, const NerfNetDims& d, const __half* wd, co
                       uint32_t n, __half* out) {
     if (n == 0) return;
     NGP_PROFILE_SCOPE(s, "nerf_mlp_forward", n);
-    FwdParams p{wd, wr, enc, coords, out, 4, tiles_of(n)};
+    FwdParams p{wd, wr, enc, coords, out, 4, tiles_of(n), nullptr};
     NERF_DISPATCH(launch_fwd, MODE_NERF, d, s, p);
 }
 
 void nerf_mlp_density(cudaStream_t s, const NerfNetDims& d, const __half* wd, const __half* enc, uint32_t n, __half* out) {
     if (n == 0) return;
     NGP_PROFILE_SCOPE(s, "nerf_mlp_density", n);
-    FwdParams p{wd, nullptr, enc, nullptr, out, 1, tiles_of(n)};
+    FwdParams p{wd, nullptr, enc, nullptr, out, 1, tiles_of(n), nullptr};
     NerfNetDims dd = d; dd.rgb_hidden = 1;
     NERF_DISPATCH(launch_fwd, MODE_DENSITY, dd, s, p);
 }
@@ -597,7 +788,7 @@ void mlp_forward(cudaStream_t s, uint32_t in_w, uint32_t nh, const __half* w, co
     if (n == 0) return;
     NGP_CHECK(out_stride % 8 == 0 && out_stride >= 16, "mlp_forward: out_stride must be a multiple of 8 and >= 16");
     NGP_PROFILE_SCOPE(s, "mlp_forward", n);
-    FwdParams p{w, nullptr, in, nullptr, out, out_stride, tiles_of(n)};
+    FwdParams p{w, nullptr, in, nullptr, out, out_stride, tiles_of(n), nullptr};
     PLAIN_DISPATCH(launch_fwd, in_w, nh, s, p);
 }
 

@@ -229,7 +229,11 @@ Trainer::~Trainer() {
 uint64_t Trainer::apply_l2_policy(cudaStream_t s) {
     if (l2_tried && l2_stream == s) return l2_window_bytes;
     l2_tried = true; l2_stream = s; l2_window_bytes = 0;
-    if (const char* e = getenv("NGP_L2_PERSIST")) if (atoi(e) == 0) return 0;
+    // OFF unless NGP_L2_PERSIST=1.  Measured on B200 at the headline config (profiles/r02_ab_l2_red.json): with the 48.8 MB window
+    // grid_forward is unchanged (0.115 ms: its gathers already hit — the bound is the L2 sector rate, not DRAM misses), grid_backward
+    // gains 1 % and Adam LOSES 24 % (0.074 -> 0.091 ms: its fp16 reads/writes of the table become persisting accesses and the
+    // carve-out takes 49 of 126 MB from the fp32 state streaming through) — 0.552 -> 0.562 ms per step overall.
+    { const char* e = getenv("NGP_L2_PERSIST"); if (!e || atoi(e) == 0) return 0; }
     int dev = 0, max_persist = 0, max_window = 0;
     if (cudaGetDevice(&dev) != cudaSuccess) return 0;
     cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, dev);

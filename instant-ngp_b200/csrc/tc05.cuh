@@ -61,6 +61,24 @@ NGP_D void tmem_ld16(uint32_t taddr, float* v) {
     for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
 }
 
+// registers -> TMEM, 32 lanes x N consecutive 32-bit columns (thread t of warp w writes lane 32*(w%4)+t).  Used to hand the
+// fp16 activations of a layer to the next layer's MMA as its A operand WITHOUT a round trip through shared memory: for
+// kind::f16 an A operand in TMEM is [M = lane][K/2 columns], two consecutive K elements packed per 32-bit column (low half
+// first) — verified numerically on B200 by tools/ubench_tc.cu.  Measured (tools/ubench_tc*.cu): tcgen05.st 758 B/cycle/SM,
+// tcgen05.ld 335 B/cycle/SM; a 128x64 epilogue (ld, relu+pack, st) takes 148 cycles into TMEM against 322 into shared memory.
+NGP_D void tmem_st16(uint32_t taddr, const uint32_t* r) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};"
+                 ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]),
+                   "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]) : "memory");
+}
+NGP_D void tmem_st32(uint32_t taddr, const uint32_t* r) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};"
+                 ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]), "r"(r[10]),
+                   "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]), "r"(r[18]), "r"(r[19]), "r"(r[20]), "r"(r[21]),
+                   "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31]) : "memory");
+}
+NGP_D void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
 // ---- UMMA descriptors ----
 // shared-memory matrix descriptor, SWIZZLE_NONE, sm_100 version field = 1 (bits 46-47)
 NGP_D uint64_t make_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
@@ -77,6 +95,16 @@ NGP_D void umma(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
         "setp.ne.b32 p, %4, 0;\n\t"
         "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
         ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// D[tmem] (+)= A[tmem] * B[smem] ("TS" form): the A operand is read from tensor memory, so the instruction's shared-memory
+// traffic is B alone.  Measured per K=16 instruction on B200: M128 N64 33.6 cycles (SS form: 50, bound by the 4 KB A read at
+// 128 B/cycle), M128 N16 10.6 cycles (SS form: 40.5).
+NGP_D void umma_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
 // arrive on an mbarrier when all previously issued MMAs of this thread have completed
 NGP_D void umma_commit(uint64_t* bar) {
@@ -97,6 +125,18 @@ template <uint32_t N>
 NGP_D void gemm_act_wT(uint32_t tmem_d, Operand a, uint32_t a_k0, Operand w, uint32_t K) {
     constexpr uint32_t idesc = make_idesc(128, N, 0, 0);
     for (uint32_t k = 0; k < K; k += 16) umma(tmem_d, desc_kmajor(a, a_k0 + k), desc_kmajor(w, k), idesc, k > 0);
+}
+// D[128 x N] = A[128 x K] * W^T with A in TMEM (packed fp16 pairs from column tmem_a on), W = [N x K] blk8 weights (K-major B)
+template <uint32_t N>
+NGP_D void gemm_tmem_wT(uint32_t tmem_d, uint32_t tmem_a, Operand w, uint32_t K) {
+    constexpr uint32_t idesc = make_idesc(128, N, 0, 0);
+    for (uint32_t k = 0; k < K; k += 16) umma_ts(tmem_d, tmem_a + (k >> 1), desc_kmajor(w, k), idesc, k > 0);
+}
+// D[128 x N] = G[128 x K] * W with G in TMEM, W = [K x N] blk8 weights read MN-major (dgrad)
+template <uint32_t N>
+NGP_D void gemm_tmem_w(uint32_t tmem_d, uint32_t tmem_g, Operand w, uint32_t K) {
+    constexpr uint32_t idesc = make_idesc(128, N, 0, 1);
+    for (uint32_t k = 0; k < K; k += 16) umma_ts(tmem_d, tmem_g + (k >> 1), desc_mnmajor(w, 0, k), idesc, k > 0);
 }
 // D[128 x N] = G[128 x K] * W, G K-major (K columns = W's rows), W = [K x N] blk8 weights read MN-major (dgrad)
 template <uint32_t N>

@@ -178,6 +178,8 @@ def test_abi_exports_every_declared_symbol():
     declared = set()
     for fn in os.listdir(inc):
         txt = open(os.path.join(inc, fn)).read()
+        if "NGP_MATH_HD" in txt:
+            continue            # ngp_b200_math.h: static inline helpers compiled into both sides, no linkage
         txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
         declared |= set(re.findall(r"\b(ngp_[a-z0-9_]+)\s*\(", txt))
     assert len(declared) >= 25
