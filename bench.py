@@ -284,6 +284,8 @@ def run_own(args):
     tb, views = make_testbed(args)
     if world > 1:
         tb.enable_data_parallel(native=os.environ.get('NGP_DP_NATIVE', '1') == '1')
+        if args.sharded_optimizer:
+            tb.dp_sharded_optimizer = True      # reduce-scatter -> Adam on 1/world of the entries -> all-gather
     batch = args.batch
 
     def barrier():
@@ -421,7 +423,7 @@ def run_own(args):
     line = {"metric": METRIC, "value": n_samples / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16 (fp32 accumulate, fp32 master weights)",
             "data": "synthetic",
-            "config": {"workload": workload_name(args), "global_batch": batch * world, "per_gpu_batch": batch, "parallelism": f"dp{world}" if world > 1 else "single",
+            "config": {"workload": workload_name(args), "global_batch": batch * world, "per_gpu_batch": batch, "parallelism": (f"dp{world}" + ("_sharded_optimizer" if args.sharded_optimizer else "")) if world > 1 else "single",
                        "pretrain_steps_untimed": args.pretrain, "samples_before_compaction_per_step": n_before / args.steps / world,
                        "rays_per_batch": tb.stats.rays_per_batch, "n_params": int(tb.n_params()), "steps_with_prefetched_rays": prefetch_hits,
                        "l2_policy": "inputs larger than L2: 256 MB image set + 24 MB table + >100 MB sample buffers touched every step",
@@ -441,6 +443,72 @@ def run_own(args):
         dist.destroy_process_group()
 
 
+def run_render(args):
+    """--render WxH: BASELINE config 5's inference leg.  The frame is cut into `world` horizontal bands, rank r renders rows
+    [r*H/world, (r+1)*H/world) with its replica of the trained parameters + bitfield (no collective on the render path); the
+    bands are then gathered to rank 0 (timed separately).  ms_per_frame = max over ranks of the band time; one JSON line on rank 0."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1")); rank = int(os.environ.get("RANK", "0")); local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    scene = importlib.import_module("instant-ngp_b200.scene")
+    W, H = (int(v) for v in args.render.lower().split("x"))
+    tb, views = make_testbed(args)
+    if world > 1:
+        tb.enable_data_parallel(native=True)
+        if args.sharded_optimizer:
+            tb.dp_sharded_optimizer = True
+    for _ in range(args.pretrain):
+        tb.train(args.batch)
+    tb.sync_inference_params()
+    torch.cuda.synchronize()
+    rows = [(r * H // world, (r + 1) * H // world) for r in range(world)]
+    y0, y1 = rows[rank]
+    f = scene.focal_px(H)
+    band = torch.empty(y1 - y0, W, 4, dtype=torch.float32, device="cuda")
+    cam = views[7 % len(views)]["xform"]
+    def frame():
+        tb.render(W, H, 1, camera_matrix=cam, focal_length=(f, f), y0=y0, y1=y1, out=band)
+    for _ in range(max(args.warmup, 2)):
+        frame()
+    def sync():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+    times = []
+    for _ in range(args.steps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        sync(); e0.record(); frame(); e1.record(); sync()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], dtype=torch.float64, device="cuda"); dist.all_reduce(t, op=dist.ReduceOp.MAX); ms = float(t.item())
+        times.append(ms)
+    # gather of the bands to rank 0 (equal band heights when world divides H)
+    gather_ms = 0.0
+    if world > 1:
+        full = [torch.empty_like(band) for _ in range(world)] if rank == 0 else None
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        for _ in range(2):
+            sync(); e0.record(); dist.gather(band, full, dst=0); e1.record(); sync()
+        gather_ms = e0.elapsed_time(e1)
+    times.sort()
+    cov = float((band[..., 3] > 0.5).float().mean())
+    if rank == 0:
+        med = times[len(times) // 2]
+        print(json.dumps({"metric": "nerf_render_ms_per_frame", "value": med, "unit": "ms/frame", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 2),
+                          "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "f16 (fp32 accumulate)", "data": "synthetic",
+                          "config": {"workload": f"render_{W}x{H}_spp1_" + workload_name(args), "row_bands": world, "rows_per_rank": y1 - y0, "pretrain_steps_untimed": args.pretrain,
+                                     "parallelism": f"tiles{world}" if world > 1 else "single"},
+                          "ms_min": times[0], "ms_max": times[-1], "Mpixels_per_s": W * H / med / 1e3, "gather_to_rank0_ms": gather_ms, "gather_bytes": W * H * 16,
+                          "band0_coverage": cov}), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -453,11 +521,15 @@ def main():
     ap.add_argument("--batch", type=int, default=BATCH)
     ap.add_argument("--log2-hashmap-size", type=int, default=19)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--sharded-optimizer", action="store_true", help="data parallel: reduce-scatter, Adam on 1/world of the entries, all-gather")
+    ap.add_argument("--render", default="", help="WxH: time the inference render, rows sharded over the ranks (BASELINE config 5), instead of training")
     ap.add_argument("--repeats", type=int, default=15, help="K-step windows timed back to back; the median is reported")
     ap.add_argument("--cpu-steps", type=int, default=3, help="timed steps of the CPU arm (a full-batch step takes seconds)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
+    elif args.render:
+        run_render(args)
     else:
         run_own(args)
 

@@ -210,6 +210,10 @@ int ngp_testbed_set_shard(ngp_testbed_t t, uint32_t rank, uint32_t world_size);
  * time: nccl_lib_path names libnccl.so.2 (NULL: the copy already loaded in the process, $NGP_NCCL_LIB, or the system one). */
 int ngp_comm_unique_id(void* out_128_bytes, const char* nccl_lib_path);
 int ngp_testbed_comm_init(ngp_testbed_t t, const void* id_128_bytes, uint32_t rank, uint32_t world_size, const char* nccl_lib_path);
+/* Sharded optimizer ("dp_sharded_optimizer" = 1, data parallel only; no reference counterpart — the reference trains on one GPU,
+ * README.md:250-252): the EMA / inference parameters of the other ranks' slices are fetched with one in-place ncclAllGather.
+ * COLLECTIVE: every rank calls it before any rank renders or saves a snapshot; a no-op otherwise. */
+int ngp_testbed_sync_inference_params(ngp_testbed_t t, void* stream);
 int ngp_testbed_stats(ngp_testbed_t t, ngp_train_stats* out);
 uint64_t ngp_testbed_n_params(ngp_testbed_t t);                                         /* Testbed::n_params python_api.cu:440 */
 uint64_t ngp_testbed_n_encoding_params(ngp_testbed_t t);                                /* Testbed::n_encoding_params python_api.cu:445 */
@@ -227,7 +231,8 @@ int ngp_msgpack_roundtrip(const void* in, uint64_t in_size, void* out, uint64_t 
 int ngp_testbed_save_snapshot(ngp_testbed_t t, void* stream, const char* path, int32_t include_optimizer_state, int32_t compress);
 int ngp_testbed_load_snapshot(ngp_testbed_t t, void* stream, const char* path);
 /* device pointers of the trainer's flat buffers (layout nerf_network.h:430-443): 0 master fp32, 1 params fp16,
- * 2 inference params fp16 (EMA), 3 gradients fp16 */
+ * 2 inference params fp16 (EMA), 3 gradients fp16, 4 / 5 Adam first / second moments fp32, 6 per-entry step counts u32,
+ * 7 EMA fp32 (NULL without an Ema optimizer) */
 int ngp_testbed_param_buffer(ngp_testbed_t t, int which, void** dev_ptr, uint64_t* n_elements);
 /* occupancy grid: 0 density grid fp32 [128^3*(max_cascade+1)], 1 bitfield u8 [128^3*8/8] */
 int ngp_testbed_density_grid(ngp_testbed_t t, int which, void** dev_ptr, uint64_t* n_bytes);
@@ -251,7 +256,8 @@ int ngp_testbed_compute_image_mse(ngp_testbed_t t, void* stream, int32_t quantiz
  * "image_linear_colors","image_stratified" (bool), "background_r/g/b" (float),
  * "sampler_lanes_per_ray" (0 automatic | 1 | 2 | 4 | 8 | 32: lanes that cooperate on one training ray; results are identical),
  * "prefetch_rays" (bool, default 1: the next step's rays are generated on a second stream beside this step's backward pass
- * and optimizer whenever the next step does not refresh the occupancy grid first; results are identical) */
+ * and optimizer whenever the next step does not refresh the occupancy grid first; results are identical),
+ * "dp_sharded_optimizer" (bool, default 0; data parallel: reduce-scatter -> Adam on 1/world of the entries -> all-gather) */
 int ngp_testbed_set_option(ngp_testbed_t t, const char* name, double value);
 /* parity hook: device pointer + capacity of an internal per-step buffer ("coords","numsteps","ray_indices","rays",
  * "counters","mlp_out","dloss","coords_compacted","loss","grid_pos","grid_idx","grid_out","mean_density",...) */

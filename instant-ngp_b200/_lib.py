@@ -110,6 +110,7 @@ SYMBOLS = {
     "ngp_testbed_set_shard": (i32, [vp, u32, u32]),
     "ngp_testbed_pending_counters": (i32, [vp, vp, vp]),
     "ngp_comm_unique_id": (i32, [vp, C.c_char_p]),
+    "ngp_testbed_sync_inference_params": (i32, [vp, vp]),
     "ngp_testbed_comm_init": (i32, [vp, vp, u32, u32, C.c_char_p]),
     "ngp_testbed_stats": (i32, [vp, C.POINTER(TrainStats)]),
     "ngp_testbed_n_params": (u64, [vp]),

@@ -356,11 +356,17 @@ int ngp_testbed_load_snapshot(ngp_testbed_t t, void* stream, const char* path) {
     t->tb.load_snapshot(S(stream), path);
     NGP_API_END
 }
+int ngp_testbed_sync_inference_params(ngp_testbed_t t, void* stream) {
+    NGP_API_BEGIN NGP_CHECK(t, "null argument"); require_device();
+    t->tb.sync_inference_params(S(stream));
+    NGP_API_END
+}
 int ngp_testbed_param_buffer(ngp_testbed_t t, int which, void** ptr, uint64_t* n) {
     NGP_API_BEGIN NGP_CHECK(t && ptr && n, "null argument");
     Trainer* tr = t->tb.trainer(); NGP_CHECK(tr, "no network loaded");
     switch (which) { case 0: *ptr = tr->master; break; case 1: *ptr = tr->params; break; case 2: *ptr = tr->inference_params; break;
-        case 3: *ptr = tr->grads; break; default: throw Error("param_buffer: which must be 0..3"); }
+        case 3: *ptr = tr->grads; break; case 4: *ptr = tr->m; break; case 5: *ptr = tr->v; break; case 6: *ptr = tr->steps; break;
+        case 7: *ptr = tr->ema; break; default: throw Error("param_buffer: which must be 0..7"); }
     *n = tr->n_params;
     NGP_API_END
 }
@@ -409,7 +415,7 @@ int ngp_testbed_debug_buffer(ngp_testbed_t t, const char* name, void** ptr, uint
     X(random_bg_color, bool) X(linear_colors, bool) X(snap_to_pixel_centers, bool) X(train_snap_to_pixel_centers, bool) X(shall_train_encoding, bool) X(shall_train_network, bool) \
     X(near_distance, float) X(density_grid_decay, float) X(render_min_transmittance, float) X(cone_angle_constant, float)         \
     X(loss_type, int) X(rgb_activation, int) X(density_activation, int) X(seed, uint64_t)                                        \
-    X(image_snap_to_pixel_centers, bool) X(image_linear_colors, bool) X(image_stratified, bool) X(sampler_lanes_per_ray, uint32_t) X(prefetch_rays, bool) X(prefetch_hits, uint32_t)
+    X(image_snap_to_pixel_centers, bool) X(image_linear_colors, bool) X(image_stratified, bool) X(sampler_lanes_per_ray, uint32_t) X(prefetch_rays, bool) X(prefetch_hits, uint32_t) X(dp_sharded_optimizer, bool)
 
 int ngp_testbed_set_option(ngp_testbed_t t, const char* name, double value) {
     NGP_API_BEGIN NGP_CHECK(t && name, "null argument");

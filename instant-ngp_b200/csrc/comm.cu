@@ -12,6 +12,8 @@ struct Api {
     int (*CommInitRank)(void**, int, NcclId, int) = nullptr;
     int (*CommDestroy)(void*) = nullptr;
     int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+    int (*ReduceScatter)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+    int (*AllGather)(const void*, void*, size_t, int, void*, cudaStream_t) = nullptr;
     const char* (*GetErrorString)(int) = nullptr;
 };
 Api& api(const char* lib_path) {
@@ -28,6 +30,9 @@ Api& api(const char* lib_path) {
         a.CommDestroy = reinterpret_cast<decltype(a.CommDestroy)>(dlsym(h, "ncclCommDestroy"));
         a.AllReduce = reinterpret_cast<decltype(a.AllReduce)>(dlsym(h, "ncclAllReduce"));
         a.GetErrorString = reinterpret_cast<decltype(a.GetErrorString)>(dlsym(h, "ncclGetErrorString"));
+        a.ReduceScatter = reinterpret_cast<decltype(a.ReduceScatter)>(dlsym(h, "ncclReduceScatter"));
+        a.AllGather = reinterpret_cast<decltype(a.AllGather)>(dlsym(h, "ncclAllGather"));
+        if (!a.ReduceScatter || !a.AllGather) err = "libnccl.so.2 lacks ncclReduceScatter / ncclAllGather";
         if (!a.GetUniqueId || !a.CommInitRank || !a.CommDestroy || !a.AllReduce || !a.GetErrorString) err = "libnccl.so.2 lacks a required symbol";
     });
     if (!err.empty()) throw Error(err);
@@ -57,6 +62,18 @@ Comm::~Comm() {
 void Comm::all_reduce_sum(void* buf, size_t count, CommDtype dtype, cudaStream_t s) {
     Api& a = api(nullptr);
     check(a, a.AllReduce(buf, buf, count, (int)dtype, /*ncclSum*/ 0, m_comm, s), "ncclAllReduce");
+}
+
+void Comm::reduce_scatter_sum(void* buf, size_t count_per_rank, CommDtype dtype, cudaStream_t s) {
+    Api& a = api(nullptr);
+    const size_t esz = dtype == COMM_F16 ? 2 : 4;
+    check(a, a.ReduceScatter(buf, static_cast<char*>(buf) + (size_t)m_rank * count_per_rank * esz, count_per_rank, (int)dtype, /*ncclSum*/ 0, m_comm, s), "ncclReduceScatter");
+}
+
+void Comm::all_gather(void* buf, size_t count_per_rank, CommDtype dtype, cudaStream_t s) {
+    Api& a = api(nullptr);
+    const size_t esz = dtype == COMM_F16 ? 2 : 4;
+    check(a, a.AllGather(static_cast<const char*>(buf) + (size_t)m_rank * count_per_rank * esz, buf, count_per_rank, (int)dtype, m_comm, s), "ncclAllGather");
 }
 
 }  // namespace ngp

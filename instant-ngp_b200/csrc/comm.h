@@ -17,6 +17,10 @@ public:
     Comm(const void* id128, int rank, int world, const char* lib_path); // ncclCommInitRank: collective over all ranks
     ~Comm();
     void all_reduce_sum(void* buf, size_t count, CommDtype dtype, cudaStream_t s);   // in place
+    // in place over a buffer of world * count_per_rank elements: rank r ends up with the sum of everybody's slice r in ITS slice r
+    void reduce_scatter_sum(void* buf, size_t count_per_rank, CommDtype dtype, cudaStream_t s);
+    // in place: every rank contributes its slice r of the buffer, all ranks end up with all slices
+    void all_gather(void* buf, size_t count_per_rank, CommDtype dtype, cudaStream_t s);
     int rank() const { return m_rank; }
     int world() const { return m_world; }
 private:

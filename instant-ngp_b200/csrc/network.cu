@@ -210,14 +210,17 @@ void Optimizer::update_hyperparams(const Json& j) {
 }
 
 Trainer::Trainer(uint64_t n, uint64_t n_matrix, const Json& optimizer_cfg) : n_params(n), n_matrix_params(n_matrix), opt(optimizer_cfg) {
-    const uint64_t n_al = next_multiple(n, 128);   // grads start 256-byte aligned behind params in the same allocation (one L2 window covers both)
-    NGP_CUDA_CHECK(cudaMalloc(&master, n * 4)); NGP_CUDA_CHECK(cudaMalloc(&params, n_al * 2 * 2)); grads = params + n_al;
+    // capacity: a multiple of 2048 entries, so that the vector splits into 1 / 2 / 4 / 8 / 16 equal, 128-entry-aligned shards for the
+    // sharded optimizer (reduce-scatter / all-gather work in place over [0, n_cap)); grads follow params in the same allocation
+    n_cap = next_multiple(n, 2048);
+    NGP_CUDA_CHECK(cudaMalloc(&master, n * 4)); NGP_CUDA_CHECK(cudaMalloc(&params, n_cap * 2 * 2)); grads = params + n_cap;
+    NGP_CUDA_CHECK(cudaMemset(params, 0, n_cap * 2 * 2));
     NGP_CUDA_CHECK(cudaMalloc(&m, n * 4)); NGP_CUDA_CHECK(cudaMalloc(&v, n * 4)); NGP_CUDA_CHECK(cudaMalloc(&steps, n * 4));
     NGP_CUDA_CHECK(cudaMemset(m, 0, n * 4)); NGP_CUDA_CHECK(cudaMemset(v, 0, n * 4)); NGP_CUDA_CHECK(cudaMemset(steps, 0, n * 4));
     NGP_CUDA_CHECK(cudaMemset(grads, 0, n * 2));
     if (opt.ema_decay > 0.0f) {
         NGP_CUDA_CHECK(cudaMalloc(&ema, n * 4)); NGP_CUDA_CHECK(cudaMemset(ema, 0, n * 4));
-        NGP_CUDA_CHECK(cudaMalloc(&inference_params, n * 2));
+        NGP_CUDA_CHECK(cudaMalloc(&inference_params, n_cap * 2)); NGP_CUDA_CHECK(cudaMemset(inference_params, 0, n_cap * 2));
     } else inference_params = params;
 }
 
@@ -256,6 +259,27 @@ uint64_t Trainer::apply_l2_policy(cudaStream_t s) {
 void Trainer::params_from_master(cudaStream_t s) {
     cast_f32_to_half(s, master, params, n_params);
     if (inference_params != params) NGP_CUDA_CHECK(cudaMemcpyAsync(inference_params, params, n_params * 2, cudaMemcpyDeviceToDevice, s));
+}
+
+// Sharded step (data parallel): the caller has reduce-scattered the gradients, so entries [start, start + count) of
+// `grads` hold the global sums; Adam (+EMA) runs on that slice only — 1/world of the HBM traffic — and the caller all-gathers the
+// fp16 parameters afterwards.  Optimizer state outside the slice is never touched on this rank (its owner keeps it).
+void Trainer::optimizer_step_shard(cudaStream_t s, float loss_scale, uint64_t start, uint64_t count) {
+    NGP_CHECK(start % 8 == 0, "optimizer_step_shard: shard start must be a multiple of 8");
+    const uint64_t end = std::min(start + count, n_params);
+    AdamHyper h{};
+    h.learning_rate = opt.current_lr; h.beta1 = opt.beta1; h.beta2 = opt.beta2; h.epsilon = opt.epsilon; h.l2_reg = opt.l2_reg;
+    h.loss_scale = loss_scale;
+    h.n_matrix_params = n_matrix_params > start ? std::min(n_matrix_params - start, end > start ? end - start : 0) : 0;
+    h.optimize_matrix = opt.optimize_matrix; h.optimize_non_matrix = opt.optimize_non_matrix;
+    h.ema_decay = opt.ema_decay; h.ema_step = opt.step_count + 1;
+    h.clear_consumed_grads = 0; grid_grads_clean = false;      // the other ranks' slices hold partial sums: the whole table is cleared before the next pass
+    if (end > start)
+        adam_step(s, h, end - start, master + start, params + start, grads + start, m + start, v + start, steps + start, ema ? ema + start : nullptr,
+                  ema ? inference_params + start : nullptr);
+    ++opt.step_count;
+    const uint32_t sc = opt.step_count;
+    if (opt.decay_interval > 0 && sc >= opt.decay_start && sc < opt.decay_end && (sc - opt.decay_start) % opt.decay_interval == 0) opt.current_lr *= opt.decay_base;
 }
 
 void Trainer::optimizer_step(cudaStream_t s, float loss_scale) {

@@ -79,7 +79,7 @@ struct Optimizer {
 };
 
 struct Trainer {
-    uint64_t n_params = 0, n_matrix_params = 0;
+    uint64_t n_params = 0, n_matrix_params = 0, n_cap = 0;   // n_cap: allocated entries of params / grads / inference_params (multiple of 2048)
     float* master = nullptr; __half* params = nullptr; __half* inference_params = nullptr; __half* grads = nullptr;
     float* m = nullptr; float* v = nullptr; uint32_t* steps = nullptr; float* ema = nullptr;
     Optimizer opt;
@@ -88,6 +88,7 @@ struct Trainer {
     Trainer(const Trainer&) = delete;
     void params_from_master(cudaStream_t s);             // fp16 copies after initialize_params
     void optimizer_step(cudaStream_t s, float loss_scale);
+    void optimizer_step_shard(cudaStream_t s, float loss_scale, uint64_t start, uint64_t count);
     bool grid_grads_clean = false;   // the hash-table part of `grads` is all zero (left so by the last optimizer step)
     // north_star: "tables pinned in B200's L2 via access-policy windows when they fit".  params and grads are ONE allocation
     // [fp16 params | fp16 grads]; `s` gets a persisting access-policy window over it (hit ratio scaled to the carve-out when the

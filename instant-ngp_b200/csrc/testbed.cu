@@ -298,6 +298,18 @@ void Testbed::comm_init(const void* id128, uint32_t rank, uint32_t world, const 
     m_prefetch_valid = false;
 }
 
+bool Testbed::sharded_step() const {
+    return dp_sharded_optimizer && m_comm && m_trainer && m_comm->world() > 1 && m_trainer->n_cap % (uint64_t)m_comm->world() == 0 &&
+           (m_trainer->n_cap / (uint64_t)m_comm->world()) % 128 == 0;
+}
+
+void Testbed::sync_inference_params(cudaStream_t s) {
+    if (!m_comm || !m_trainer || !m_inference_stale) return;
+    if (m_trainer->inference_params != m_trainer->params)
+        m_comm->all_gather(m_trainer->inference_params, m_trainer->n_cap / (uint64_t)m_comm->world(), COMM_F16, s);
+    m_inference_stale = false;
+}
+
 void Testbed::pending_counters(uint32_t* measured, uint32_t* measured_before) {
     NGP_CHECK(m_pending_batch > 0 && m_mode == MODE_TB_NERF, "pending_counters: no Nerf training step in flight (call train_begin first)");
     NGP_CUDA_CHECK(cudaEventSynchronize(m_ev_counters));
@@ -308,7 +320,15 @@ void Testbed::train_end(cudaStream_t s, uint32_t measured_override, uint32_t mea
     NGP_CHECK(m_pending_batch > 0, "train_end without train_begin");
     const uint32_t target = m_pending_batch; m_pending_batch = 0;
     if (m_mode == MODE_TB_SDF && m_sdf_step_skipped) return;   // train_sdf does nothing when the data set is smaller than the batch (testbed_sdf.cu:1293)
-    m_trainer->optimizer_step(s, LOSS_SCALE);   // testbed_nerf.cu:3678 / testbed_image.cu:283
+    if (m_mode == MODE_TB_NERF && sharded_step()) {
+        // reduce-scatter happened in train_nerf_step: this rank's slice of `grads` holds the global sums
+        const uint64_t shard = m_trainer->n_cap / (uint64_t)m_comm->world();
+        m_trainer->optimizer_step_shard(s, LOSS_SCALE, shard * m_comm->rank(), shard);
+        m_comm->all_gather(m_trainer->params, shard, COMM_F16, s);      // the next forward pass (ordered behind it on s) reads every slice
+        m_inference_stale = true;
+    } else {
+        m_trainer->optimizer_step(s, LOSS_SCALE);   // testbed_nerf.cu:3678 / testbed_image.cu:283
+    }
     ++m_training_step;
     if (m_mode == MODE_TB_IMAGE || m_mode == MODE_TB_SDF) {
         // the host waits only for the loss read-back (every 16th step, testbed.cu:4349-4353); otherwise it runs ahead of the device
@@ -493,7 +513,16 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
     }
     nerf_fill_rollover(s, target, &sb.counters[2], lb.dloss_doutput, lb.coords_compacted, lb.enc_out, lb.enc_width);   // :4061-4069
     // forward(compacted) + backward(EGradientMode::Overwrite) (:4077-4078)
-    if (m_comm) {
+    if (m_comm && sharded_step()) {
+        // sharded optimizer: ONE in-place reduce-scatter of the whole (padded) gradient vector on the communication stream; Adam on
+        // this rank's slice and the parameter all-gather follow in train_end
+        m_nerf_net->forward_backward_encoded(s, m_trainer->params, lb.coords_compacted, target, lb.dloss_doutput, m_trainer->grads, m_ev_after_mlp, m_trainer->grid_grads_clean);
+        NGP_CUDA_CHECK(cudaEventRecord(m_ev_slice, s));
+        NGP_CUDA_CHECK(cudaStreamWaitEvent(m_comm_stream, m_ev_slice, 0));
+        m_comm->reduce_scatter_sum(m_trainer->grads, m_trainer->n_cap / (uint64_t)m_comm->world(), COMM_F16, m_comm_stream);
+        NGP_CUDA_CHECK(cudaEventRecord(m_ev_comm_done, m_comm_stream));
+        NGP_CUDA_CHECK(cudaStreamWaitEvent(s, m_ev_comm_done, 0));
+    } else if (m_comm) {
         // every finished slice of the gradient vector (MLP weights, then one hash level chunk at a time) is summed over the ranks
         // on the communication stream while the next chunk is still being scattered; Adam waits for the last one
         __half* grads = m_trainer->grads;
@@ -599,6 +628,7 @@ void Testbed::render(cudaStream_t s, const float* camera_matrix, const float* fo
                      float* rgba_out, bool out_is_device, float* depth_out) {
     NGP_CHECK(m_mode == MODE_TB_NERF && m_nerf_net && m_trainer, "render: NeRF network not initialised");
     NGP_CHECK(w > 0 && h > 0 && y0 >= 0 && y1 <= h && y0 < y1 && spp >= 1, "render: bad resolution / row band");
+    NGP_CHECK(!m_inference_stale, "render: sharded optimizer — call sync_inference_params (collective, every rank) first");
     const uint32_t n_pixels = (uint32_t)w * (uint32_t)(y1 - y0);
     const uint32_t n_pad = (uint32_t)next_multiple(n_pixels, BATCH_GRANULARITY);
     RaysSoa rays[3];

@@ -100,6 +100,12 @@ public:
     // the occupancy bitfield and the rng only, not on the weights); same samples either way, see launch_ray_prefetch()
     bool prefetch_rays = true;
     uint32_t prefetch_hits = 0;   // read-only: steps whose rays came from a prefetch
+    // data parallel only: reduce-scatter the gradients, run Adam(+EMA) on this rank's 1/world of the entries, all-gather the fp16
+    // parameters (instead of all-reduce + the full optimizer on every rank).  Same arithmetic per entry; the EMA (inference)
+    // parameters of the other ranks' slices are fetched by sync_inference_params() — a COLLECTIVE every rank must call before
+    // any of them renders or saves a snapshot (pyngp does it inside render / save_snapshot).
+    bool dp_sharded_optimizer = false;
+    void sync_inference_params(cudaStream_t s);
     Aabb aabb{{0, 0, 0}, {1, 1, 1}}, render_aabb{{0, 0, 0}, {1, 1, 1}};
     int render_lens_mode = LENS_PERSPECTIVE; float render_lens_params[4] = {0, 0, 0, 0};   // m_nerf.render_lens (set_camera_to_training_view)
     const std::vector<ImageMeta>& training_views() const { return m_host_metas; }
@@ -153,6 +159,8 @@ private:
     DeviceBuffer m_mlp_out, m_dloss, m_coords_compacted, m_loss, m_ray_scratch, m_compacted_numsteps, m_loss_sum, m_t_before;
     cudaStream_t m_aux_stream = nullptr; cudaEvent_t m_ev_counters = nullptr, m_ev_prefetch = nullptr, m_ev_after_mlp = nullptr;
     uint32_t* m_host_counters = nullptr;   // pinned: [0..3] counters, [4] loss sum, [5..6] all-reduced (before, measured)
+    bool m_inference_stale = false;       // sharded optimizer: inference_params outside this rank's slice are behind
+    bool sharded_step() const;            // dp_sharded_optimizer && a communicator && the vector splits evenly over the ranks
     std::unique_ptr<Comm> m_comm; cudaStream_t m_comm_stream = nullptr; cudaEvent_t m_ev_slice = nullptr, m_ev_comm_done = nullptr, m_ev_dp_counters = nullptr;
     DeviceBuffer m_dp_counters;
     cudaStream_t m_copy_stream = nullptr; cudaEvent_t m_ev_copy_gate = nullptr, m_ev_copy_done = nullptr; bool m_copy_pending = false;

@@ -53,7 +53,7 @@ def _stream():
 
 
 _BOOL_OPTS = {"random_bg_color", "linear_colors", "snap_to_pixel_centers", "train_snap_to_pixel_centers", "shall_train_encoding", "shall_train_network",
-              "image_snap_to_pixel_centers", "image_linear_colors", "image_stratified", "prefetch_rays"}
+              "image_snap_to_pixel_centers", "image_linear_colors", "image_stratified", "prefetch_rays", "dp_sharded_optimizer"}
 _FLOAT_OPTS = {"near_distance", "density_grid_decay", "render_min_transmittance", "cone_angle_constant"}
 _INT_OPTS = {"loss_type", "rgb_activation", "density_activation", "seed", "sampler_lanes_per_ray", "prefetch_hits"}
 
@@ -305,7 +305,12 @@ class Testbed:
         return lib().ngp_testbed_n_encoding_params(self._h)
 
     # ---- snapshots (python_api.cu:446-449) ----
+    def sync_inference_params(self):
+        """COLLECTIVE (sharded optimizer only, otherwise a no-op): fetch the other ranks' slices of the EMA / inference parameters"""
+        check(lib().ngp_testbed_sync_inference_params(self._h, _stream()))
+
     def save_snapshot(self, path, include_optimizer_state=False, compress=True):
+        self.sync_inference_params()
         check(lib().ngp_testbed_save_snapshot(self._h, _stream(), os.fspath(path).encode(), int(include_optimizer_state), int(compress)))
 
     def load_snapshot(self, path):
@@ -410,7 +415,11 @@ class Testbed:
     def param_buffer(self, which):
         ptr, n = C.c_void_p(), C.c_uint64()
         check(lib().ngp_testbed_param_buffer(self._h, which, C.byref(ptr), C.byref(n)))
-        return _wrap(ptr.value, n.value, torch.float32 if which == 0 else torch.float16)
+        # 0 fp32 master, 1 fp16 params, 2 fp16 inference (EMA) params, 3 fp16 grads, 4 / 5 Adam first / second moments (fp32),
+        # 6 per-entry step counts (u32 as int32), 7 fp32 EMA (null without an Ema optimizer)
+        if not ptr.value:
+            return None
+        return _wrap(ptr.value, n.value, {0: torch.float32, 4: torch.float32, 5: torch.float32, 6: torch.int32, 7: torch.float32}.get(which, torch.float16))
 
     def density_grid(self, which=0):
         ptr, n = C.c_void_p(), C.c_uint64()
@@ -431,6 +440,7 @@ class Testbed:
                out=None, return_depth=False):
         """float32 [rows, W, 4] linear premultiplied RGBA of rows [y0, y1) (python_api.cu:127-205, headless)."""
         y1 = height if y1 is None else y1
+        self.sync_inference_params()      # no-op unless the sharded optimizer left other ranks' EMA slices behind (then: collective)
         cam = (C.c_float * 12)(*[float(x) for x in np.asarray(camera_matrix, np.float32).reshape(-1)])
         fl = (C.c_float * 2)(*focal_length)
         sc = (C.c_float * 2)(*screen_center)

@@ -87,5 +87,71 @@ def test_sharded_gradients_sum_to_the_global_step():
     assert res["rpb"] % 256 == 0 and res["rpb"] >= 256
 
 
+def _worker_sharded(rank, world, port):
+    """sharded optimizer (csrc/testbed.cu sharded_step / Trainer::optimizer_step_shard): reduce-scatter of the padded fp16 gradient vector,
+    Adam + EMA on this rank's slice with the matrix-parameter boundary moved into slice coordinates, all-gather of the fp16 parameters
+    == all-reduce + the full optimizer on every rank, entry for entry"""
+    sys.path.insert(0, ROOT)
+    from oracle import ref_api as ref
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    n, nm = 50000 + 8 * 3, 7168
+    n_cap = (n + 2047) // 2048 * 2048; shard = n_cap // world
+    assert shard % 128 == 0
+    rng = np.random.default_rng(5)                                   # same initial state on every rank
+    master = rng.normal(0, 0.1, n).astype(np.float32); params = master.astype(np.float16)
+    m = np.zeros(n, np.float32); v = np.zeros(n, np.float32); steps = np.zeros(n, np.uint32)
+    full = [a.copy() for a in (master, params, m, v, steps)]
+    params_cap = np.zeros(n_cap, np.float16); params_cap[:n] = params
+    for step in range(3):
+        local = np.random.default_rng(100 + 10 * step + rank)       # this rank's gradient
+        g = np.zeros(n_cap, np.float32)
+        g[:n] = local.normal(0, 1, n) * (local.uniform(size=n) < 0.3)
+        # --- dense path: all-reduce, full Adam (what every rank does without the option) ---
+        t = torch.from_numpy(g.copy()); dist.all_reduce(t)
+        g_sum = t.numpy().astype(np.float16)
+        ref.adam_step(ref.AdamCfg(1e-2, 0.9, 0.99, 1e-15, 1e-6, 128.0, nm, 1, 1), full[0], full[1], g_sum[:n].copy(), full[2], full[3], full[4])
+        # --- sharded path: reduce each slice to its owner, Adam on [start, end), all-gather ---
+        mine = None
+        for r in range(world):
+            sl = torch.from_numpy(g[r * shard:(r + 1) * shard].copy()); dist.reduce(sl, dst=r)
+            if r == rank:
+                mine = sl.numpy().astype(np.float16)
+        start = rank * shard; end = min(start + shard, n)
+        nm_local = max(0, min(nm - start, end - start)) if nm > start else 0
+        if end > start:
+            sm, sp, smm, sv, ss = master[start:end].copy(), params_cap[start:end].copy(), m[start:end].copy(), v[start:end].copy(), steps[start:end].copy()
+            ref.adam_step(ref.AdamCfg(1e-2, 0.9, 0.99, 1e-15, 1e-6, 128.0, nm_local, 1, 1), sm, sp, mine[:end - start].copy(), smm, sv, ss)
+            master[start:end], params_cap[start:end], m[start:end], v[start:end], steps[start:end] = sm, sp, smm, sv, ss
+        parts = [torch.zeros(shard, dtype=torch.float16) for _ in range(world)]
+        dist.all_gather(parts, torch.from_numpy(params_cap[start:start + shard].copy()))
+        params_cap = torch.cat(parts).numpy()
+    ok = bool(np.array_equal(params_cap[:n].view(np.uint16), full[1].view(np.uint16))) and bool(np.array_equal(steps[start:end], full[4][start:end])) \
+        and bool(np.array_equal(master[start:end].view(np.uint32), full[0][start:end].view(np.uint32)))
+    flag = torch.tensor([int(ok)]); dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    if rank == 0:
+        print("RESULT " + json.dumps(dict(ok=int(flag[0]), shard=shard, n_cap=n_cap)), flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_sharded_optimizer_equals_allreduce_plus_full_adam():
+    port = 30600 + os.getpid() % 1000
+    env = dict(os.environ, OMP_NUM_THREADS="2")
+    procs = [subprocess.Popen([sys.executable, os.path.abspath(__file__), "--worker-sharded", str(r), "2", str(port)], stdout=subprocess.PIPE,
+                              stderr=subprocess.STDOUT, text=True, env=env) for r in range(2)]
+    outs = []
+    for p in procs:
+        out, _ = p.communicate(timeout=300)
+        outs.append(out)
+        assert p.returncode == 0, out[-2000:]
+    line = [l for l in outs[0].splitlines() if l.startswith("RESULT ")]
+    assert line, outs[0][-2000:]
+    res = json.loads(line[0][7:])
+    assert res["ok"] == 1 and res["shard"] * 2 == res["n_cap"], res
+
+
 if __name__ == "__main__" and len(sys.argv) >= 5 and sys.argv[1] == "--worker":
     _worker(int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4]))
+if __name__ == "__main__" and len(sys.argv) >= 5 and sys.argv[1] == "--worker-sharded":
+    _worker_sharded(int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4]))

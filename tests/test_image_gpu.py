@@ -64,3 +64,46 @@ def test_image_training_converges(ngp):
     mse1 = tb.compute_image_mse()
     assert mse1 < 0.05 * mse0 and mse1 < 2e-3, (mse0, mse1)
     assert tb.training_step == 300 and tb.loss > 0
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# BASELINE config 2: data/image/albert.exr (staged by tools/stage_data.py into baseline/_data/, 1024x1024 RGBA float32),
+# 2-D HashGrid 16x2 T = 2^24 + 2x64 FullyFusedMLP (configs/image/base.json), 2^18 pixels per batch
+# ---------------------------------------------------------------------------------------------------------------------
+ALBERT = __import__("os").path.join(__import__("os").path.dirname(__import__("os").path.dirname(__import__("os").path.abspath(__file__))),
+                                   "baseline", "_data", "albert", "albert_rgba_f32.npy")
+ALBERT_CFG = {**IMG_CFG, "encoding": {"otype": "HashGrid", "n_levels": 16, "n_features_per_level": 2, "log2_hashmap_size": 24, "base_resolution": 16,
+                                      "per_level_scale": 2.0}}
+
+
+@pytest.mark.skipif(not __import__("os").path.exists(ALBERT), reason="albert.exr not staged (python tools/stage_data.py in the build container)")
+def test_config2_albert_t24_batch_2pow18(ngp, ref):
+    """one training step at the configuration BASELINE.json names: positions bit-exact, bilinear / nearest targets, L2 gradients vs the oracle
+    on the real image; then 60 steps must cut the full-image MSE (compute_image_mse over all 2^20 pixels) by 10x"""
+    pyngp = importlib.import_module("instant-ngp_b200.pyngp")
+    img = np.load(ALBERT)
+    assert img.shape == (1024, 1024, 4) and img.dtype == np.float32
+    tb = pyngp.Testbed(pyngp.TestbedMode.Image)
+    tb.set_image(img)
+    tb.reload_network_from_json(ALBERT_CFG)
+    assert tb.n_params() > 250_000_000           # 2-D, 16 levels, T = 2^24: ~280 M parameters (SURVEY section 8)
+    n = 1 << 18
+    mse0 = tb.compute_image_mse()
+    tb.train(n)
+    pos = tb.debug_tensor("image_pos", torch.float32, n * 2).cpu().numpy().reshape(n, 2)
+    tgt = tb.debug_tensor("image_target", torch.float32, n * 3).cpu().numpy().reshape(n, 3)
+    rpos = np.zeros((n, 2), np.float32)
+    ref.lib().ref_image_positions(ref.u64(1337), ref.u64(1), ref.u32(n), ref.i32(1), ref.P(rpos))
+    rtgt = np.zeros((n, 3), np.float32)
+    ref.lib().ref_image_eval(ref.P(img), ref.i32(1024), ref.i32(1024), ref.u32(n), ref.P(rpos), ref.P(rtgt), ref.i32(1), ref.i32(0))
+    assert np.array_equal(pos, rpos)
+    np.testing.assert_allclose(tgt, rtgt, rtol=1e-5, atol=1e-6)
+    out = tb.debug_tensor("image_out", torch.float16, n * 16).cpu().numpy().reshape(n, 16)
+    dl = tb.debug_tensor("image_dl", torch.float16, n * 16).cpu().numpy().reshape(n, 16)
+    rdl = np.zeros((n, 16), np.float16)
+    ref.lib().ref_l2_loss(ref.P(out), 16, ref.P(rtgt), n, 128.0, ref.P(rdl))
+    np.testing.assert_allclose(dl.astype(np.float32), rdl.astype(np.float32), rtol=2e-3, atol=1e-8)
+    for _ in range(60):
+        tb.train(n)
+    mse1 = tb.compute_image_mse()
+    assert mse1 < 0.1 * mse0, (mse0, mse1)

@@ -29,12 +29,12 @@ def env(ngp, ref):
     return dict(pyngp=pyngp, scene=scene, views=views, images=images, keep=keep)
 
 
-def _testbed(env, lanes=0, prefetch=True):
+def _testbed(env, lanes=0, prefetch=True, cfg=None):
     tb = env["pyngp"].Testbed(env["pyngp"].TestbedMode.Nerf)
     tb.sampler_lanes_per_ray = lanes     # 0 automatic; 1 / 2 / 4 / 8 / 32 lanes cooperate on one ray (identical results)
     tb.prefetch_rays = prefetch          # next step's rays generated beside this step's backward pass (identical results)
     tb.set_nerf_dataset(env["views"], aabb_scale=1)
-    tb.reload_network_from_json(SMALL_CFG)
+    tb.reload_network_from_json(cfg or SMALL_CFG)
     return tb
 
 
@@ -79,24 +79,22 @@ def test_occupancy_grid_first_update(env, ref):
     assert ((grid == -1) == (grid0 == -1)).all()
 
 
-def _step_and_capture(tb, ref, env, n_warm):
+def _step_and_capture(tb, ref, env, n_warm, batch=BATCH):
     for _ in range(n_warm):
-        tb.train(BATCH)
+        tb.train(batch)
     st = tb.stats
     rpb, mb = st.rays_per_batch, st.measured_batch_size_before_compaction
-    max_samples = BATCH * 16
+    max_samples = batch * 16
     max_inference = max_samples if mb == 0 else (min(mb, max_samples) + 255) // 256 * 256
     step = st.training_step
-    tb.train(BATCH)
+    tb.train(batch)
     return rpb, max_inference, step
 
 
-@pytest.mark.parametrize("n_warm,lanes,prefetch", [(w, l, True) for w in (0, 5) for l in (1, 2, 4, 8, 32)] + [(37, 0, True), (37, 0, False), (51, 8, True)])
-def test_sampler_and_loss_bit_exact_compaction(env, ref, n_warm, lanes, prefetch):
-    """n_warm >= 33 and odd: the captured step does not refresh the occupancy grid, so with prefetch its rays were generated
-    on the second stream during the step before"""
-    tb = _testbed(env, lanes, prefetch)
-    rpb, max_inf, step = _step_and_capture(tb, ref, env, n_warm)
+def _check_step_against_oracle(tb, ref, env, n_warm, prefetch, batch):
+    """one captured training step: rays, per-ray counts, every sample coordinate, compacted counts and coordinates bit-exact;
+    loss gradients within 2e-3 of their scale; fill_rollover semantics"""
+    rpb, max_inf, step = _step_and_capture(tb, ref, env, n_warm, batch)
     if n_warm > 32:
         assert (tb.prefetch_hits > 0) == prefetch
     aabb = ref.make_aabb((0, 0, 0), (1, 1, 1))
@@ -117,24 +115,48 @@ def test_sampler_and_loss_bit_exact_compaction(env, ref, n_warm, lanes, prefetch
     mlp_out = tb.debug_tensor("mlp_out", torch.float16, n_written * 4).cpu().numpy().reshape(n_written, 4)
     mean_density = float(tb.debug_tensor("mean_density", torch.float32, 1).cpu().numpy()[0])
     cfg = ref.LossCfg(4, 2, 3, 1, 0, 1, (ref.f32 * 3)(0, 0, 0), 128.0, 0.1, mean_density)
-    lo = ref.compute_loss(rpb, aabb, 1337, skip, BATCH, nr, cfg, env["images"], mlp_out, o["ray_indices"], o["rays"], o["numsteps"], o["coords"])
+    lo = ref.compute_loss(rpb, aabb, 1337, skip, batch, nr, cfg, env["images"], mlp_out, o["ray_indices"], o["rays"], o["numsteps"], o["coords"])
     assert c[2] == lo["compacted_counter"]
     gns = tb.debug_tensor("numsteps", torch.int32, nr * 2).cpu().numpy().view(np.uint32).reshape(nr, 2)
     assert np.array_equal(gns, lo["numsteps"][:nr])
-    nc = int(min(c[2], BATCH))
-    gcc = tb.debug_tensor("coords_compacted", torch.float32, BATCH * 7).cpu().numpy().reshape(BATCH, 7)
+    nc = int(min(c[2], batch))
+    gcc = tb.debug_tensor("coords_compacted", torch.float32, batch * 7).cpu().numpy().reshape(batch, 7)
     assert np.array_equal(gcc[:nc], lo["coords_compacted"][:nc])
-    gdl = tb.debug_tensor("dloss", torch.float16, BATCH * 4).cpu().numpy().reshape(BATCH, 4).astype(np.float32)
+    gdl = tb.debug_tensor("dloss", torch.float16, batch * 4).cpu().numpy().reshape(batch, 4).astype(np.float32)
     rdl = lo["dloss"][:nc].astype(np.float32)
     scale = np.abs(rdl).max()
     assert np.abs(gdl[:nc] - rdl).max() <= 2e-3 * scale + 1e-7, (np.abs(gdl[:nc] - rdl).max(), scale)
     gl = tb.debug_tensor("loss", torch.float32, rpb).cpu().numpy()
     np.testing.assert_allclose(gl[:nr], lo["loss"][:nr], rtol=1e-3, atol=1e-9)
-    # fill_rollover: rows [nc, BATCH) are cyclic copies, gradients scaled by nc/BATCH
-    if nc < BATCH:
-        src = np.arange(nc, BATCH) % nc
+    # fill_rollover: rows [nc, batch) are cyclic copies, gradients scaled by nc/batch
+    if nc < batch:
+        src = np.arange(nc, batch) % nc
         assert np.array_equal(gcc[nc:], gcc[src])
-        np.testing.assert_allclose(gdl[nc:], gdl[src] * (nc / BATCH), rtol=2e-3, atol=1e-7)
+        np.testing.assert_allclose(gdl[nc:], gdl[src] * (nc / batch), rtol=2e-3, atol=1e-7)
+    return nr, n_written, nc
+
+
+@pytest.mark.parametrize("n_warm,lanes,prefetch", [(w, l, True) for w in (0, 5) for l in (1, 2, 4, 8, 32)] + [(37, 0, True), (37, 0, False), (51, 8, True)])
+def test_sampler_and_loss_bit_exact_compaction(env, ref, n_warm, lanes, prefetch):
+    """n_warm >= 33 and odd: the captured step does not refresh the occupancy grid, so with prefetch its rays were generated
+    on the second stream during the step before"""
+    tb = _testbed(env, lanes, prefetch)
+    _check_step_against_oracle(tb, ref, env, n_warm, prefetch, BATCH)
+
+
+HEADLINE_CFG = {**SMALL_CFG, "encoding": {**SMALL_CFG["encoding"], "log2_hashmap_size": 19}}
+
+
+@pytest.mark.parametrize("n_warm", [2, 37])
+def test_headline_shape_step_bit_exact(env, ref, n_warm):
+    """The step of BASELINE.json's headline config — HashGrid 16x2 T = 2^19, batch 2^18 (the view set stays small: the batch and the
+    table size are what the kernels see) — against the oracle: same bit-exact bars as the small-shape test.  n_warm 2: the untrained
+    grid (every cell occupied, ~16 batch sizes of samples before compaction, the inference cap max_samples is hit); n_warm 37: sparsified
+    grid, automatic lane choice, prefetched rays."""
+    batch = 1 << 18
+    tb = _testbed(env, 0, True, HEADLINE_CFG)
+    nr, n_written, nc = _check_step_against_oracle(tb, ref, env, n_warm, True, batch)
+    assert n_written >= batch // 2 and nc > 0
 
 
 @pytest.mark.parametrize("lanes", [1, 8, 32])
@@ -162,6 +184,48 @@ def test_sampler_with_cascades_and_cone_angle(env, ref, lanes):
     gcoords = tb.debug_tensor("coords", torch.float32, n_written * 7).cpu().numpy().reshape(n_written, 7)
     assert np.array_equal(gcoords.view(np.uint32), o["coords"][:n_written].view(np.uint32))
     assert ns_gpu.max() > 0
+
+
+FOX_LENS = (0.0578421, -0.0805099, -0.000980296, 0.00015575)          # k1, k2, p1, p2 of data/nerf/fox/transforms.json:6-9
+FOX_PRINCIPAL = (554.558 / 1080.0, 965.268 / 1920.0)                  # cx / w, cy / h (:10-13)
+
+
+@pytest.mark.parametrize("lanes", [1, 8])
+def test_opencv_lens_rays_and_samples_bit_exact(env, ref, lanes):
+    """Config 3 (fox) trains every ray through iterative_opencv_lens_undistortion (common_device.cuh:289-377, up to 100 Newton
+    iterations) with an off-centre principal point, 4 occupancy cascades (aabb_scale 8) and cone angle 1/256.  Same views as the other
+    tests but declared with fox's lens: the ray origins / directions (undistorted on the GPU in sampler_classify_kernel), the cells
+    mark_untrained_density_grid keeps (pos_to_uv applies the forward distortion), per-ray counts and every sample coordinate must equal
+    the oracle's restatement bit for bit."""
+    pyngp = env["pyngp"]
+    views = [{**v, "lens_mode": 1, "lens_params": FOX_LENS, "principal_point": FOX_PRINCIPAL} for v in env["views"]]
+    images, keep = ref.images_from_views(views)
+    tb = pyngp.Testbed(pyngp.TestbedMode.Nerf)
+    tb.sampler_lanes_per_ray = lanes
+    tb.set_nerf_dataset(views, aabb_scale=8)
+    tb.reload_network_from_json(SMALL_CFG)
+    assert tb.training_view(0)["lens_mode"] == 1
+    rpb, max_inf, step = _step_and_capture(tb, ref, env, 2)
+    NC = 128 ** 3
+    grid0 = ref.mark_untrained(np.zeros(NC * 4, np.float32), images)
+    grid = tb.density_grid(0).cpu().numpy()
+    assert grid.size == NC * 4 and np.array_equal(grid == -1, grid0 == -1)
+    aabb = ref.make_aabb((-3.5,) * 3, (4.5,) * 3)
+    bf = tb.density_grid(1).cpu().numpy()
+    o = ref.generate_training_samples(rpb, aabb, max_inf, 1337, 1 + step * (1 << 32), images, bf, 3, True, 1.0 / 256.0)
+    c = tb.debug_tensor("counters", torch.int32, 4).cpu().numpy().view(np.uint32)
+    assert int(c[0]) == int(o["ray_counter"]) and int(c[1]) == int(o["numsteps_counter"])
+    nr = int(c[0])
+    assert nr > 0
+    assert np.array_equal(tb.debug_tensor("ray_indices", torch.int32, nr).cpu().numpy().view(np.uint32), o["ray_indices"][:nr])
+    grays = tb.debug_tensor("rays", torch.float32, nr * 6).cpu().numpy().reshape(nr, 6)
+    assert np.array_equal(grays.view(np.uint32), o["rays"][:nr].view(np.uint32))
+    # the lens did bend the rays: the same pixels through a pinhole give other directions
+    o_pin = ref.generate_training_samples(rpb, aabb, max_inf, 1337, 1 + step * (1 << 32), env["images"], bf, 3, True, 1.0 / 256.0)
+    assert not np.array_equal(o_pin["rays"][:8], o["rays"][:8])
+    n_written = int(o["numsteps"][:nr, 0].sum())
+    gcoords = tb.debug_tensor("coords", torch.float32, n_written * 7).cpu().numpy().reshape(n_written, 7)
+    assert np.array_equal(gcoords.view(np.uint32), o["coords"][:n_written].view(np.uint32))
 
 
 def test_marcher_variants_train_identically(env):
