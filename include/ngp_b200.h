@@ -88,6 +88,19 @@ int ngp_nerf_network_initialize_params(ngp_nerf_network_t n, void* stream, uint6
 int ngp_nerf_network_inference(ngp_nerf_network_t n, void* stream, const void* dev_params_fp16, const void* dev_coords, uint32_t count, void* dev_out);
 /* density() (:337-353): pos fp32 [n][pos_stride]; out fp16 [n] */
 int ngp_nerf_network_density(ngp_nerf_network_t n, void* stream, const void* dev_params_fp16, const void* dev_pos, uint32_t pos_stride, uint32_t count, void* dev_out);
+/* NO COUNTERPART IN THE REFERENCE — added for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same computation, same kernels and same arguments as
+ * ngp_nerf_network_inference, but the call ALLOCATES NOTHING: the encoder-output scratch that the regular entry point keeps in a
+ * grow-on-demand cudaMalloc'ed buffer lives in a file-scope static __device__ array (csrc/noalloc.cu) of
+ * NGP_NOALLOC_MAX_SAMPLES x 32 fp16 = 1 MiB, held by every GPU that loads the library until the process exits.
+ * count must be a multiple of 128 and <= NGP_NOALLOC_MAX_SAMPLES (larger counts fail with a clear error: split the batch).
+ * Every call shares that array (it keeps the last call's contents; the call overwrites all it reads, nothing needs clearing):
+ * calls that overlap on the GPU — different streams or host threads — RACE on it and must be serialised by the caller.
+ * Per-kernel profiling (ngp_profile_enable) must be off for the no-allocation guarantee. */
+#define NGP_NOALLOC_MAX_SAMPLES 16384u
+uint32_t ngp_noalloc_max_samples(void);
+int ngp_nerf_network_inference_noalloc(ngp_nerf_network_t n, void* stream, const void* dev_params_fp16, const void* dev_coords, uint32_t count,
+                                       void* dev_out);
 /* forward_impl + backward_impl with EGradientMode::Overwrite (:179-335): dL_dout fp16 [n][4]; grads fp16, param shaped */
 int ngp_nerf_network_forward_backward(ngp_nerf_network_t n, void* stream, const void* dev_params_fp16, const void* dev_coords, uint32_t count,
                                       const void* dev_dL_dout, void* dev_grads_fp16);

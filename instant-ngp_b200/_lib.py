@@ -76,6 +76,8 @@ SYMBOLS = {
     "ngp_nerf_network_layout": (i32, [vp, C.POINTER(u64), C.POINTER(u64), C.POINTER(u64), C.POINTER(u64)]),
     "ngp_nerf_network_initialize_params": (i32, [vp, vp, u64, vp]),
     "ngp_nerf_network_inference": (i32, [vp, vp, vp, vp, u32, vp]),
+    "ngp_nerf_network_inference_noalloc": (i32, [vp, vp, vp, vp, u32, vp]),
+    "ngp_noalloc_max_samples": (u32, []),
     "ngp_nerf_network_density": (i32, [vp, vp, vp, vp, u32, u32, vp]),
     "ngp_nerf_network_forward_backward": (i32, [vp, vp, vp, vp, u32, vp, vp]),
     "ngp_encoded_mlp_create": (i32, [cp, u32, u32, C.POINTER(vp)]),

@@ -35,6 +35,12 @@ static void require_device() {
     if (e != cudaSuccess || n == 0) { cudaGetLastError(); throw Error("ngp_b200: no CUDA device available (this library has no CPU fallback)"); }
 }
 
+// used by noalloc.cu (the allocation-free inference entry point lives beside its static scratch array)
+namespace ngp {
+NerfNetwork* capi_nerf_network(ngp_nerf_network_t h) { return &h->net; }
+void capi_set_last_error(const char* msg) { g_last_error = msg ? msg : "unknown error"; }
+}
+
 extern "C" {
 
 const char* ngp_last_error(void) { return g_last_error.c_str(); }
