@@ -394,19 +394,24 @@ def run_own(args):
             per_unit = inst[name]["warp_inst_per_unit"]
             ach = per_unit * units / t_launch
             row.update(bound="issue", achieved=ach / 1e9, peak=issue_peak / 1e9, unit="Gwarp-inst/s", frac=ach / issue_peak, per_unit=per_unit, traffic=traffic.get(name))
-        if name == "grid_forward":      # the metric's own roofline: fraction of the measured random-gather rate of this GPU's L2 / HBM
-            gathers = corners * units / t_launch
-            row["l2_gather"] = {"achieved_Ggathers_per_s": gathers / 1e9, "peak_Ggathers_per_s": g.value / 1e9, "frac": gathers / g.value,
-                                "peak_how": f"ngp_microbench_l2_gather over {table_bytes} B (table size), 32 independent 4-byte loads in flight per thread"}
+        if name in ("grid_forward", "grid_backward"):
+            # the metric's own roofline ("hash-enc Gpoints/s vs L2 BW"): L2 sectors this launch requested per second — sectors per point
+            # from the committed ncu capture (profiles/instructions.json; a warp's gathers coalesce when neighbouring samples share cells,
+            # so sectors, not gathers, are what the memory system sees) x points / measured time — against the random-sector rate of this
+            # GPU measured just now (ngp_microbench_l2_gather: one sector per gather, nothing coalesces) => <= 1 by construction
             row["gpoints_per_s"] = units / t_launch / 1e9
-        if name == "grid_backward":     # scattered fp16x2 reductions: 8 corners x L entries per point; best case = every x-neighbour pair in one lane
-            ent = corners * units / t_launch
-            peak_ent = max(r1.value, 2.0 * r2.value)
-            row["l2_red"] = {"achieved_Gentries_per_s": ent / 1e9, "peak_Gentries_per_s": peak_ent / 1e9, "frac": ent / peak_ent,
-                             "red_f16x2_Glanes_per_s": r1.value / 1e9, "red_v2_f16x2_Glanes_per_s": r2.value / 1e9,
-                             "peak_how": "max(ngp_microbench_l2_red vec 1, 2 x vec 2): scattered red.global.add lanes/s over a table-sized buffer; "
-                                         "2 entries per lane = both x-neighbour corners merged, the most this access pattern allows"}
-            row["gpoints_per_s"] = units / t_launch / 1e9
+            spu = inst.get(name, {}).get("lts_sectors_per_unit")
+            if spu:
+                rate = spu * units / t_launch
+                row["l2_sectors"] = {"achieved_Gsectors_per_s": rate / 1e9, "peak_Gsectors_per_s": g.value / 1e9, "frac": rate / g.value,
+                                     "achieved_GB_per_s": rate * 32 / 1e9, "sectors_per_point": spu, "ncu_pct_of_peak": inst[name].get("ncu_pct_of_peak"),
+                                     "peak_how": f"ngp_microbench_l2_gather over {table_bytes} B (table size): random 4-byte loads, 32 in flight per thread, 1 sector each"}
+            if name == "grid_backward":
+                row["l2_sectors"] = dict(row.get("l2_sectors", {}), red_f16x2_Glanes_per_s=r1.value / 1e9, red_v2_f16x2_Glanes_per_s=r2.value / 1e9,
+                                         note="scattered red.global.add lanes/s of ngp_microbench_l2_red, for reference: REDs to one sector from one warp "
+                                              "instruction merge, so the kernel's sector rate can exceed it")
+        if name in inst and "ncu_pct_of_peak" in inst[name] and "l2_sectors" not in row:
+            row["ncu_pct_of_peak"] = inst[name]["ncu_pct_of_peak"]
         kernels[name] = row
     step_ms_prof = sum(k["ms_per_step"] for k in kernels.values())
     cand = [k for k in kernels if "achieved" in kernels[k]]
@@ -415,7 +420,7 @@ def run_own(args):
     src = {"tensor": ", sustained bf16", "hbm": ", copy bandwidth", "issue": f": 148 SMs x 4 schedulers x {sm_hz / 1e6:.0f} MHz sampled under load"}[roof["bound"]]
     roof.update(kernel=top, share_of_step=kernels[top]["ms_per_step"] / step_ms_prof, avg_ms=kernels[top]["avg_ms"],
                 peak_source=(peaks["source"] if roof["bound"] != "issue" else "issue rate") + src)
-    for extra in ("l2_gather", "l2_red"):
+    for extra in ("l2_sectors",):
         if extra in kernels[top]:
             roof[extra] = kernels[top][extra]
 
