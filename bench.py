@@ -428,7 +428,7 @@ def run_own(args):
     line = {"metric": METRIC, "value": n_samples / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16 (fp32 accumulate, fp32 master weights)",
             "data": "synthetic",
-            "config": {"workload": workload_name(args), "global_batch": batch * world, "per_gpu_batch": batch, "parallelism": (f"dp{world}" + ("_sharded_optimizer" if args.sharded_optimizer else "")) if world > 1 else "single",
+            "config": {"workload": workload_name(args), "global_batch": batch * world, "per_gpu_batch": batch, "parallelism": (f"dp{world}" + ("_sharded_optimizer" if args.sharded_optimizer else "_dense_allreduce")) if world > 1 else "single",
                        "pretrain_steps_untimed": args.pretrain, "samples_before_compaction_per_step": n_before / args.steps / world,
                        "rays_per_batch": tb.stats.rays_per_batch, "n_params": int(tb.n_params()), "steps_with_prefetched_rays": prefetch_hits,
                        "l2_policy": "inputs larger than L2: 256 MB image set + 24 MB table + >100 MB sample buffers touched every step",
@@ -526,7 +526,10 @@ def main():
     ap.add_argument("--batch", type=int, default=BATCH)
     ap.add_argument("--log2-hashmap-size", type=int, default=19)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--sharded-optimizer", action="store_true", help="data parallel: reduce-scatter, Adam on 1/world of the entries, all-gather")
+    ap.add_argument("--sharded-optimizer", dest="sharded_optimizer", action="store_true", default=True,
+                    help="data parallel (default): reduce-scatter, Adam on 1/world of the entries, all-gather — measured faster than the dense all-reduce at 2 and 8 GPUs "
+                         "(profiles/r02_scaling.json)")
+    ap.add_argument("--dense-allreduce", dest="sharded_optimizer", action="store_false", help="data parallel: one dense all-reduce + the full optimizer on every rank")
     ap.add_argument("--render", default="", help="WxH: time the inference render, rows sharded over the ranks (BASELINE config 5), instead of training")
     ap.add_argument("--repeats", type=int, default=15, help="K-step windows timed back to back; the median is reported")
     ap.add_argument("--cpu-steps", type=int, default=3, help="timed steps of the CPU arm (a full-batch step takes seconds)")

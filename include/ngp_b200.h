@@ -30,6 +30,9 @@ uint64_t ngp_kernel_launch_count(void);
  * {"<kernel group>": {"count": launches, "ms": total}} written to buf (NUL terminated) */
 void ngp_profile_enable(int on);
 int ngp_profile_report(char* buf, uint64_t buf_size, int reset);
+/* the same records as an absolute timeline, [["kernel group", start_us, duration_us], ...] relative to the first record since the last
+ * reset (both streams: shows how the ray prefetch overlaps the training stream); call before ngp_profile_report(.., reset = 1) */
+int ngp_profile_timeline(char* buf, uint64_t buf_size);
 
 /* Roofline denominators of the hash-grid kernels, measured on the current device (no reference
  * counterpart — the reference publishes no roofline): random 4-byte gathers per second with 32 loads in flight per

@@ -58,6 +58,7 @@ SYMBOLS = {
     "ngp_kernel_launch_count": (u64, []),
     "ngp_profile_enable": (None, [i32]),
     "ngp_profile_report": (i32, [cp, u64, i32]),
+    "ngp_profile_timeline": (i32, [cp, u64]),
     "ngp_microbench_l2_gather": (i32, [vp, u64, u32, C.POINTER(C.c_double)]),
     "ngp_microbench_l2_red": (i32, [vp, u64, i32, u32, C.POINTER(C.c_double)]),
     "ngp_encoding_create": (i32, [cp, u32, C.POINTER(vp)]),

@@ -55,6 +55,13 @@ int ngp_profile_report(char* buf, uint64_t buf_size, int reset) {
     NGP_API_END
 }
 
+int ngp_profile_timeline(char* buf, uint64_t buf_size) {
+    NGP_API_BEGIN NGP_CHECK(buf && buf_size > 2, "null argument");
+    const std::string r = profile_timeline_json();
+    NGP_CHECK(r.size() + 1 <= buf_size, "profile timeline buffer too small");
+    memcpy(buf, r.c_str(), r.size() + 1);
+    NGP_API_END
+}
 int ngp_microbench_l2_gather(void* stream, uint64_t buffer_bytes, uint32_t reps, double* out) {
     NGP_API_BEGIN NGP_CHECK(out, "null argument"); require_device();
     *out = microbench_l2_gather(S(stream), buffer_bytes, reps);

@@ -11,6 +11,8 @@
 #include "tc05.cuh"
 #include <cstdio>
 #include <cstdlib>
+#include <vector>
+#include <algorithm>
 
 namespace ngp {
 using namespace tc;
@@ -428,6 +430,7 @@ struct BwdParams {
     __half* dL_denc;      // nullable
     float* wgrad;         // [n_density_params + n_rgb_params] fp32, atomically accumulated
     uint32_t n_tiles;
+    unsigned long long* probe;   // debug (NGP_MLP_PROBE=1): per CTA [4] = %globaltimer at start / after the prologue / after the tile loop / at exit; null otherwise
 };
 
 template <uint32_t PW, uint32_t DH, uint32_t RH, int MODE>
@@ -544,6 +547,8 @@ __global__ void __launch_bounds__(128) mlp_backward_kernel(const BwdParams p) {
     uint64_t* bar_full = reinterpret_cast<uint64_t*>(smem + L.bars);
     uint64_t* bar_mma = bar_full + 1;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_full + 2);
+    auto stamp = [&](uint32_t i) { if (p.probe && tid == 0) { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); p.probe[(size_t)blockIdx.x * 4 + i] = t; } };
+    stamp(0);
 
     if (tid == 0) { mbar_init(bar_full, 1); mbar_init(bar_mma, 1); mbar_fence_init(); }
     if (warp == 0) tmem_alloc<Cfg::TMEM_COLS>(tmem_slot);
@@ -559,6 +564,7 @@ __global__ void __launch_bounds__(128) mlp_backward_kernel(const BwdParams p) {
     __half* r0 = reinterpret_cast<__half*>(smem + L.r0);
     __half* go = reinterpret_cast<__half*>(smem + L.go);
 
+    stamp(1);
     StageSync stage{bar_mma, 0};
     uint32_t full_parity = 0, it = 0;
     if (tid == 0 && blockIdx.x < p.n_tiles) {
@@ -637,6 +643,7 @@ __global__ void __launch_bounds__(128) mlp_backward_kernel(const BwdParams p) {
     fence_before_sync();
     __syncthreads();
     fence_after_sync();
+    stamp(2);
     if (it > 0) {
         float* wg = p.wgrad;
         flush_wgrad<PW, false>(tmem_row, Cfg::ACC_D0, wg, PW, tid); wg += MLP_WIDTH * PW;
@@ -650,6 +657,7 @@ __global__ void __launch_bounds__(128) mlp_backward_kernel(const BwdParams p) {
     }
     fence_before_sync();
     __syncthreads();
+    stamp(3);
     if (warp == 0) tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
 }
 
@@ -716,6 +724,22 @@ static void launch_fwd(cudaStream_t s, const FwdParams& p) {
 template <uint32_t PW, uint32_t DH, uint32_t RH, int MODE>
 static void launch_bwd(cudaStream_t s, const BwdParams& p) {
     const BwdCfg<PW, DH, RH, MODE> L;
+    static const bool probe = getenv("NGP_MLP_PROBE") != nullptr;
+    if (probe && p.dL_denc && p.n_tiles >= 1024) {   // debug: where the kernel's wall time goes, from per-CTA %globaltimer stamps (ns), to stderr
+        auto k = mlp_backward_kernel<PW, DH, RH, MODE, true>;
+        const uint32_t grid = persistent_grid(k, L.total, BwdCfg<PW, DH, RH, MODE>::TMEM_COLS, p.n_tiles);
+        BwdParams q = p; unsigned long long* d = nullptr; std::vector<unsigned long long> h((size_t)grid * 4);
+        NGP_CUDA_CHECK(cudaMalloc(&d, h.size() * 8)); q.probe = d;
+        k<<<grid, 128, L.total, s>>>(q);
+        NGP_POST_LAUNCH();
+        NGP_CUDA_CHECK(cudaMemcpyAsync(h.data(), d, h.size() * 8, cudaMemcpyDeviceToHost, s)); NGP_CUDA_CHECK(cudaStreamSynchronize(s)); cudaFree(d);
+        unsigned long long t0 = ~0ull, t3 = 0; double pro = 0, loop = 0, fl = 0, start_spread = 0;
+        for (uint32_t b = 0; b < grid; ++b) { t0 = std::min(t0, h[b * 4]); t3 = std::max(t3, h[b * 4 + 3]); }
+        for (uint32_t b = 0; b < grid; ++b) { pro += h[b * 4 + 1] - h[b * 4]; loop += h[b * 4 + 2] - h[b * 4 + 1]; fl += h[b * 4 + 3] - h[b * 4 + 2]; start_spread = std::max(start_spread, (double)(h[b * 4] - t0)); }
+        fprintf(stderr, "[ngp] mlp_backward probe (grid %u, %u tiles): first start -> last exit %.1f us; per CTA mean: prologue %.1f us, tile loop %.1f us, wgrad flush %.1f us; last CTA started %.1f us after the first\n",
+                grid, p.n_tiles, (t3 - t0) * 1e-3, pro / grid * 1e-3, loop / grid * 1e-3, fl / grid * 1e-3, start_spread * 1e-3);
+        return;
+    }
     if (p.dL_denc) {
         auto k = mlp_backward_kernel<PW, DH, RH, MODE, true>;
         const uint32_t grid = persistent_grid(k, L.total, BwdCfg<PW, DH, RH, MODE>::TMEM_COLS, p.n_tiles);
@@ -780,7 +804,7 @@ void nerf_mlp_backward(cudaStream_t s, const NerfNetDims& d, const __half* wd, c
                        uint32_t n, const __half* dL_dout, __half* dL_denc, float* wgrad) {
     if (n == 0) return;
     NGP_PROFILE_SCOPE(s, "nerf_mlp_backward", n);
-    BwdParams p{wd, wr, enc, coords, dL_dout, 4, dL_denc, wgrad, tiles_of(n)};
+    BwdParams p{wd, wr, enc, coords, dL_dout, 4, dL_denc, wgrad, tiles_of(n), nullptr};
     NERF_DISPATCH(launch_bwd, MODE_NERF, d, s, p);
 }
 
@@ -797,7 +821,7 @@ void mlp_backward(cudaStream_t s, uint32_t in_w, uint32_t nh, const __half* w, c
     if (n == 0) return;
     NGP_CHECK(dout_stride % 8 == 0 && dout_stride >= 16, "mlp_backward: dout_stride must be a multiple of 8 and >= 16");
     NGP_PROFILE_SCOPE(s, "mlp_backward", n);
-    BwdParams p{w, nullptr, in, nullptr, dL_dout, dout_stride, dL_din, wgrad, tiles_of(n)};
+    BwdParams p{w, nullptr, in, nullptr, dL_dout, dout_stride, dL_din, wgrad, tiles_of(n), nullptr};
     PLAIN_DISPATCH(launch_bwd, in_w, nh, s, p);
 }
 

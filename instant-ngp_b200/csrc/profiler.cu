@@ -43,4 +43,19 @@ std::string profile_report_json(bool reset) {
     if (reset) { for (auto& r : g_recs) { g_pool.push_back(r.a); g_pool.push_back(r.b); } g_recs.clear(); }
     return out;
 }
+// absolute timeline of the recorded scopes (debug / tools): [["name", start_us, duration_us], ...] relative to the first record;
+// events of different streams are comparable, so the overlap of the ray prefetch with the training stream shows
+std::string profile_timeline_json() {
+    cudaDeviceSynchronize();
+    std::lock_guard<std::mutex> l(g_mu);
+    std::string out = "[";
+    bool first = true;
+    for (auto& r : g_recs) {
+        float t0 = 0.f, d = 0.f;
+        if (cudaEventElapsedTime(&t0, g_recs[0].a, r.a) != cudaSuccess || cudaEventElapsedTime(&d, r.a, r.b) != cudaSuccess) { cudaGetLastError(); continue; }
+        if (!first) out += ", "; first = false;
+        out += "[\"" + g_names[r.name_id] + "\", " + std::to_string(t0 * 1e3) + ", " + std::to_string(d * 1e3) + "]";
+    }
+    return out + "]";
+}
 }  // namespace ngp

@@ -11,6 +11,7 @@ struct ProfileScope {
     cudaStream_t s; int slot;
 };
 void profile_enable(bool on);
-std::string profile_report_json(bool reset);   // {"name": {"count": n, "ms": total, "units": total}, ...}; synchronises the device
+std::string profile_report_json(bool reset);
+std::string profile_timeline_json();            // [["name", start_us, duration_us], ...] of the records since the last reset   // {"name": {"count": n, "ms": total, "units": total}, ...}; synchronises the device
 }
 #define NGP_PROFILE_SCOPE(stream, ...) ngp::ProfileScope _ngp_prof_scope((stream), __VA_ARGS__)
