@@ -273,6 +273,8 @@ int ngp_testbed_compute_image_mse(ngp_testbed_t t, void* stream, int32_t quantiz
  * "sampler_lanes_per_ray" (0 automatic | 1 | 2 | 4 | 8 | 32: lanes that cooperate on one training ray; results are identical),
  * "prefetch_rays" (bool, default 1: the next step's rays are generated on a second stream beside this step's backward pass
  * and optimizer whenever the next step does not refresh the occupancy grid first; results are identical),
+ * "device_control_law" (bool, default 1: the rays_per_batch control law is ALSO evaluated on the device so that the next step's rays are
+ * generated without waiting for the host to read this step's counters; results are identical),
  * "dp_sharded_optimizer" (bool, default 0; data parallel: reduce-scatter -> Adam on 1/world of the entries -> all-gather) */
 int ngp_testbed_set_option(ngp_testbed_t t, const char* name, double value);
 /* parity hook: device pointer + capacity of an internal per-step buffer ("coords","numsteps","ray_indices","rays",

@@ -428,7 +428,7 @@ int ngp_testbed_debug_buffer(ngp_testbed_t t, const char* name, void** ptr, uint
     X(random_bg_color, bool) X(linear_colors, bool) X(snap_to_pixel_centers, bool) X(train_snap_to_pixel_centers, bool) X(shall_train_encoding, bool) X(shall_train_network, bool) \
     X(near_distance, float) X(density_grid_decay, float) X(render_min_transmittance, float) X(cone_angle_constant, float)         \
     X(loss_type, int) X(rgb_activation, int) X(density_activation, int) X(seed, uint64_t)                                        \
-    X(image_snap_to_pixel_centers, bool) X(image_linear_colors, bool) X(image_stratified, bool) X(sampler_lanes_per_ray, uint32_t) X(prefetch_rays, bool) X(prefetch_hits, uint32_t) X(dp_sharded_optimizer, bool)
+    X(image_snap_to_pixel_centers, bool) X(image_linear_colors, bool) X(image_stratified, bool) X(sampler_lanes_per_ray, uint32_t) X(prefetch_rays, bool) X(prefetch_hits, uint32_t) X(dp_sharded_optimizer, bool) X(device_control_law, bool)
 
 int ngp_testbed_set_option(ngp_testbed_t t, const char* name, double value) {
     NGP_API_BEGIN NGP_CHECK(t && name, "null argument");

@@ -29,7 +29,7 @@ NGP_D uint32_t block_exclusive_scan(uint32_t v, uint32_t& total) {
 }
 
 // one block: in-place exclusive scan of up to 2 arrays of block totals; grand totals written to out0/out1 (optional)
-__global__ void __launch_bounds__(1024) scan_block_totals_kernel(uint32_t n, uint32_t* a, uint32_t* b, uint32_t* out_a, uint32_t* out_b, bool accumulate_b) {
+NGP_D void scan_block_totals(uint32_t n, uint32_t* a, uint32_t* b, uint32_t* out_a, uint32_t* out_b, bool accumulate_b) {
     __shared__ uint32_t sh[2][32];
     uint32_t carry_a = 0, carry_b = 0;
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -61,6 +61,37 @@ __global__ void __launch_bounds__(1024) scan_block_totals_kernel(uint32_t n, uin
         if (out_a) *out_a = carry_a;
         if (out_b) { if (accumulate_b) *out_b += carry_b; else *out_b = carry_b; }
     }
+}
+
+__global__ void __launch_bounds__(1024) scan_block_totals_kernel(uint32_t n, uint32_t* a, uint32_t* b, uint32_t* out_a, uint32_t* out_b, bool accumulate_b) {
+    scan_block_totals(n, a, b, out_a, out_b, accumulate_b);
+}
+// the same over ceil(dyn->n_rays / rays_per_block) block totals (device-side step parameters)
+__global__ void __launch_bounds__(1024) scan_block_totals_dyn_kernel(const StepParams* __restrict__ dyn, uint32_t rays_per_block, uint32_t* a, uint32_t* b, uint32_t* out_a) {
+    scan_block_totals((dyn->n_rays + rays_per_block - 1) / rays_per_block, a, b, out_a, nullptr, false);
+}
+NGP_D uint32_t dyn_rays(const SamplerBuffers& b, uint32_t n) { return b.dyn ? b.dyn->n_rays : n; }
+NGP_D uint32_t dyn_samples(const SamplerBuffers& b, uint32_t m) { return b.dyn ? b.dyn->max_inference : m; }
+NGP_D uint32_t dyn_scratch(const SamplerBuffers& b) { return b.dyn ? b.dyn->scratch_per_ray : b.scratch_per_ray; }
+
+// NerfCounters::update_after_training + the inference size of the next step (testbed_nerf.cu:3583-3609,3900-3930), on the device; the same
+// fp32 operations in the same order as Testbed::train_end evaluates on the host (no contraction: --fmad=false), hence the same integers
+__global__ void control_law_kernel(const uint32_t* __restrict__ counters, uint32_t rays_per_batch, uint32_t target, uint32_t rays_bound, uint32_t samples_bound,
+                                   StepParams* __restrict__ out) {
+    const uint32_t before = counters[1], measured = counters[2];
+    StepParams p{0u, 0u, 0u, 1u};
+    if (before != 0u && measured != 0u) {
+        uint32_t r = (uint32_t)((float)rays_per_batch * (float)target / (float)measured);
+        r = min((r + BATCH_GRANULARITY - 1u) / BATCH_GRANULARITY * BATCH_GRANULARITY, 1u << 18);
+        const uint32_t max_samples = target * 16u;
+        const uint32_t mi = (min(before, max_samples) + BATCH_GRANULARITY - 1u) / BATCH_GRANULARITY * BATCH_GRANULARITY;
+        if (r != 0u && r <= rays_bound && mi <= samples_bound) { p.n_rays = r; p.max_inference = mi; p.scratch_per_ray = min(NERF_STEPS, max_samples / r); p.overflow = 0u; }
+    }
+    *out = p;
+}
+void nerf_control_law(cudaStream_t s, const uint32_t* counters, uint32_t rays_per_batch, uint32_t target, uint32_t rays_bound, uint32_t samples_bound, StepParams* out) {
+    control_law_kernel<<<1, 1, 0, s>>>(counters, rays_per_batch, target, rays_bound, samples_bound, out);
+    NGP_POST_LAUNCH();
 }
 
 // =================================================================================================================
@@ -633,6 +664,7 @@ __global__ void __launch_bounds__(128) sampler_classify_kernel(uint32_t n_rays, 
                                                                bool snap, float cone_angle_constant, uint32_t ray_offset, uint32_t n_rays_global, uint32_t rays_per_block,
                                                                SamplerBuffers b) {
     constexpr uint32_t Q = 4;                                            // lanes per ray: the coarse test is split four ways
+    if (b.dyn) { n_rays = b.dyn->n_rays; n_rays_global = n_rays; }       // device-side step parameters (single rank: offset 0)
     const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, i = tid / Q, part = tid % Q;
     if (tid < (n_rays + rays_per_block - 1) / rays_per_block) { b.block_steps[tid] = 0; b.block_rays[tid] = 0; }   // totals are accumulated by the walk
     bool candidate = false;
@@ -681,7 +713,8 @@ __global__ void __launch_bounds__(SCAN_BLOCK) sampler_count_group_kernel(uint32_
     const float* rt = b.ray_tmp + (size_t)i * 8;
     const V3 o = ld3(rt), du = ld3(rt + 3);
     const float startt = rt[6]; const Cone cone(rt[7]);
-    SampleLog log{b.sample_scratch + (size_t)i * b.scratch_per_ray, b.scratch_per_ray, b.sample_pool, b.pool_slots, &b.counters[3], NO_SLOT};
+    const uint32_t spr = dyn_scratch(b);
+    SampleLog log{b.sample_scratch + (size_t)i * spr, spr, b.sample_pool, b.pool_slots, &b.counters[3], NO_SLOT};
     const uint32_t numsteps = march_training_ray_group<G, false, FLAT, K>(o, normalize3(du), startt, cone, aabb, bitfield, max_mip, NERF_STEPS, nullptr, lane, gshift, gmask, &log);
     if (lane == 0) {
         b.overflow_slot[i] = log.slot; b.numsteps_all[i] = numsteps;
@@ -693,6 +726,8 @@ template <uint32_t G, bool FLAT>
 __global__ void __launch_bounds__(SCAN_BLOCK) sampler_write_group_kernel(uint32_t n_rays, Aabb aabb, uint32_t max_samples, const uint8_t* __restrict__ bitfield,
                                                                          uint32_t max_mip, SamplerBuffers b) {
     constexpr uint32_t RPB = SCAN_BLOCK / G;
+    n_rays = dyn_rays(b, n_rays); max_samples = dyn_samples(b, max_samples);
+    const uint32_t spr = dyn_scratch(b);
     const uint32_t lane = threadIdx.x % G, gshift = (threadIdx.x & 31u) / G * G;
     const uint32_t gmask = G == 32 ? 0xffffffffu : (((1u << G) - 1u) << gshift);
     const uint32_t i = blockIdx.x * RPB + threadIdx.x / G;
@@ -716,10 +751,10 @@ __global__ void __launch_bounds__(SCAN_BLOCK) sampler_write_group_kernel(uint32_
             r[0] = o.x; r[1] = o.y; r[2] = o.z; r[3] = du.x; r[4] = du.y; r[5] = du.z;
             b.numsteps[ray_idx * 2 + 0] = numsteps; b.numsteps[ray_idx * 2 + 1] = base;
         }
-        if (numsteps > b.scratch_per_ray) slot = b.overflow_slot[i];
+        if (numsteps > spr) slot = b.overflow_slot[i];
     }
     // rays whose samples the counting walk logged are expanded by sampler_expand_kernel; the few that outgrew window and pool walk again
-    const bool logged = keep && (numsteps <= b.scratch_per_ray || slot < b.pool_slots);
+    const bool logged = keep && (numsteps <= spr || slot < b.pool_slots);
     if (!keep || logged) return;
     const float* rt = b.ray_tmp + (size_t)i * 8;
     march_training_ray_group<G, true, FLAT>(o, normalize3(du), rt[6], Cone(rt[7]), aabb, bitfield, max_mip, numsteps, b.coords + (size_t)base * 7, lane, gshift, gmask);
@@ -730,6 +765,8 @@ __global__ void __launch_bounds__(SCAN_BLOCK) sampler_write_group_kernel(uint32_
 __global__ void __launch_bounds__(256) sampler_expand_kernel(uint32_t max_samples, Aabb aabb, SamplerBuffers b) {
     __shared__ __align__(16) float stage[256 * 7];
     const uint32_t sidx = blockIdx.x * blockDim.x + threadIdx.x;
+    max_samples = dyn_samples(b, max_samples);
+    const uint32_t spr = dyn_scratch(b);
     const uint32_t n_kept = b.counters[0];
     if (n_kept == 0) return;
     const uint32_t last = n_kept - 1;
@@ -743,11 +780,11 @@ __global__ void __launch_bounds__(256) sampler_expand_kernel(uint32_t max_sample
         }
         const uint32_t numsteps = b.numsteps[lo * 2 + 0], k = sidx - b.numsteps[lo * 2 + 1];
         const uint32_t i = b.ray_indices[lo];
-        const uint32_t slot = numsteps > b.scratch_per_ray ? b.overflow_slot[i] : NO_SLOT;
+        const uint32_t slot = numsteps > spr ? b.overflow_slot[i] : NO_SLOT;
         // (rays that outgrew window and pool were written by the re-walk in sampler_write_group_kernel)
-        mine = k < numsteps && (numsteps <= b.scratch_per_ray || slot < b.pool_slots);
+        mine = k < numsteps && (numsteps <= spr || slot < b.pool_slots);
         if (mine) {
-            const SampleLog log{b.sample_scratch + (size_t)i * b.scratch_per_ray, b.scratch_per_ray, b.sample_pool, b.pool_slots, nullptr, slot};
+            const SampleLog log{b.sample_scratch + (size_t)i * spr, spr, b.sample_pool, b.pool_slots, nullptr, slot};
             const float* r = b.rays + (size_t)lo * 6;
             const V3 o = ld3(r), d = normalize3(ld3(r + 3)), wd = warp_direction(d);
             const float2 td = *log.at(k);
@@ -781,6 +818,7 @@ void nerf_generate_training_samples(cudaStream_t s, uint32_t n_rays, Aabb aabb, 
     NGP_PROFILE_SCOPE(s, "sampler", n_rays);
     const uint32_t G = b.lanes_per_ray ? b.lanes_per_ray : nerf_sampler_lanes_per_ray(n_rays);
     NGP_CHECK(G == 1 || G == 2 || G == 4 || G == 8 || G == 32, "sampler_lanes_per_ray must be 0 (automatic), 1, 2, 4, 8 or 32");
+    NGP_CHECK(!b.dyn || G != 1, "device-side step parameters need a group marcher (lanes per ray > 1)");
     uint32_t K = G == 32 ? 1u : 8u / G;                         // 8 candidates per round (32 with a whole warp per ray)
     if (const char* e = getenv("NGP_SAMPLER_K")) K = (uint32_t)atoi(e);
     const bool flat = cone_angle_constant <= 1e-5f && max_mip == 0;
@@ -803,7 +841,8 @@ void nerf_generate_training_samples(cudaStream_t s, uint32_t n_rays, Aabb aabb, 
     else if (G == 4) { if (K == 1) NGP_SAMPLER_COUNT_F(4, 1); else if (K == 4) NGP_SAMPLER_COUNT_F(4, 4); else NGP_SAMPLER_COUNT_F(4, 2); }
     else { if (K == 8) NGP_SAMPLER_COUNT_F(2, 8); else NGP_SAMPLER_COUNT_F(2, 4); }
     NGP_POST_LAUNCH();
-    scan_block_totals_kernel<<<1, 1024, 0, s>>>(blocks, b.block_steps, b.block_rays, &b.counters[1], nullptr, false);
+    if (b.dyn) scan_block_totals_dyn_kernel<<<1, 1024, 0, s>>>(b.dyn, SCAN_BLOCK / G, b.block_steps, b.block_rays, &b.counters[1]);
+    else scan_block_totals_kernel<<<1, 1024, 0, s>>>(blocks, b.block_steps, b.block_rays, &b.counters[1], nullptr, false);
     NGP_POST_LAUNCH();
     if (G == 1) { if (flat) sampler_write_kernel<true><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, max_samples, bitfield, max_mip, b);
                   else sampler_write_kernel<false><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, max_samples, bitfield, max_mip, b); }

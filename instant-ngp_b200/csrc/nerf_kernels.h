@@ -16,6 +16,17 @@ void nerf_update_bitfield(cudaStream_t s, const float* grid, uint32_t n_cascades
 // 32^3 coarse cells of the unit cube, bit set if the cell or one of its 26 neighbours holds an occupied fine cell (mip 2 of the bitfield)
 void nerf_build_coarse_occupancy(cudaStream_t s, const uint8_t* bitfield, uint32_t* coarse /* [1024] */);
 
+// Device-side step parameters.  The rays of step N+1 need rays_per_batch(N+1), which the control law (NerfCounters::update_after_training,
+// testbed_nerf.cu:3583-3609) derives from the sample counters of step N.  Waiting for the HOST to read those counters before the next
+// sampler can start costs a round trip on the critical path (measured: the training stream idled 65-75 us per 530 us step,
+// profiles/r02_timeline_before.txt).  nerf_control_law evaluates the same arithmetic on the device right behind the loss kernel; the sampler
+// for step N+1 is enqueued BEFORE the host knows the result, with grids sized for the bounds, and reads the actual counts from here
+// (SamplerBuffers::dyn).  overflow = 1: a count exceeded its bound (or was 0) and nothing was generated — the host, which evaluates the
+// same law when the counters arrive, sees that too and samples inline.
+struct StepParams { uint32_t n_rays, max_inference, scratch_per_ray, overflow; };
+void nerf_control_law(cudaStream_t s, const uint32_t* counters, uint32_t rays_per_batch, uint32_t target_batch_size, uint32_t rays_bound,
+                      uint32_t samples_bound, StepParams* out_dev);
+
 // ---- training sampler (testbed_nerf.cu:1382-1658), deterministic ray-order compaction ----
 struct SamplerBuffers {
     // per generated ray slot [n_rays]
@@ -36,6 +47,9 @@ struct SamplerBuffers {
     const uint32_t* coarse;     // 32^3-bit dilated coarse occupancy of the unit cube (nerf_build_coarse_occupancy) or nullptr: every ray is walked
     uint32_t* cand_list;        // [n_rays] indices of the rays to walk; counters[4] = how many
     uint32_t lanes_per_ray;     // 0: choose from n_rays (nerf_sampler_lanes_per_ray); 1 / 4 / 8 / 32: forced (tests compare the variants)
+    // non-null (group marchers only): n_rays / max_samples / scratch_per_ray come from device memory, the n_rays and max_samples
+    // arguments of nerf_generate_training_samples are then upper bounds that size the grids
+    const StepParams* dyn;
 };
 uint32_t nerf_sampler_lanes_per_ray(uint32_t n_rays);
 void nerf_generate_training_samples(cudaStream_t s, uint32_t n_rays, Aabb aabb, uint32_t max_samples, uint32_t n_rays_total, Pcg32 rng,

@@ -40,6 +40,7 @@ Testbed::~Testbed() {
     if (m_ev_counters) cudaEventDestroy(m_ev_counters);
     if (m_ev_prefetch) cudaEventDestroy(m_ev_prefetch);
     if (m_ev_after_mlp) cudaEventDestroy(m_ev_after_mlp);
+    if (m_ev_after_loss) cudaEventDestroy(m_ev_after_loss);
     if (m_comm_stream) { cudaStreamSynchronize(m_comm_stream); cudaStreamDestroy(m_comm_stream); }
     if (m_copy_stream) { cudaStreamSynchronize(m_copy_stream); cudaStreamDestroy(m_copy_stream); }
     for (cudaEvent_t e : {m_ev_copy_gate, m_ev_copy_done}) if (e) cudaEventDestroy(e);
@@ -93,7 +94,7 @@ void Testbed::set_nerf_dataset(cudaStream_t s, uint32_t n_images, const HostImag
     if (m_aux_stream) NGP_CUDA_CHECK(cudaStreamSynchronize(m_aux_stream));   // a ray prefetch in flight reads the old images
     if (m_copy_stream) NGP_CUDA_CHECK(cudaStreamSynchronize(m_copy_stream));
     m_copy_pending = false;
-    m_prefetch_valid = false; ++m_dataset_version; m_all_images_u8 = true;
+    m_prefetch_valid = false; m_early_prefetch = false; ++m_dataset_version; m_all_images_u8 = true;
     for (void* p : m_image_buffers) cudaFree(p);
     m_image_buffers.clear(); m_image_bytes.clear();
     m_frame_has_mask.assign(n_images, false);
@@ -148,7 +149,7 @@ void Testbed::load_nerf_post(cudaStream_t s, int aabb_scale) {
 void Testbed::reset(bool reset_density_grid) {
     NGP_CHECK(m_have_config, "reset: no network config loaded");
     NGP_CUDA_CHECK(cudaDeviceSynchronize());
-    m_prefetch_valid = false;
+    m_prefetch_valid = false; m_early_prefetch = false;
     reset_network(reset_density_grid);
 }
 
@@ -359,7 +360,16 @@ void Testbed::train_end(cudaStream_t s, uint32_t measured_override, uint32_t mea
     }
     m_rays_per_batch = (uint32_t)((float)m_rays_per_batch * (float)target / (float)m_measured);
     m_rays_per_batch = std::min((uint32_t)next_multiple(m_rays_per_batch, BATCH_GRANULARITY), 1u << 18);
-    launch_ray_prefetch(s, target);
+    if (m_early_prefetch) {
+        // the next step's sampler is already running (launch_early_prefetch): it is valid if the law evaluated here gives counts within the
+        // bounds its grids were sized for (the device evaluated the same arithmetic and generated nothing otherwise)
+        m_early_prefetch = false;
+        const uint32_t mi = max_inference_samples(target);
+        m_prefetch_key = sampler_key(m_rays_per_batch, mi, target);
+        m_prefetch_valid = m_rays_per_batch <= m_early_rays_bound && mi <= m_early_samples_bound && m_early_dataset_version == m_dataset_version;
+    } else {
+        launch_ray_prefetch(s, target);
+    }
     // No host wait for the optimizer: the control law only needed the counters (already here), and everything that consumes
     // the new weights is ordered behind them on `s`.  The host so runs half a step ahead and the device never idles between
     // steps.  Only the loss read-back (every 16th step) has to wait for its reduction.
@@ -449,7 +459,25 @@ void Testbed::launch_ray_prefetch(cudaStream_t s, uint32_t target) {
     const SamplerBuffers sb = sampler_buffers(m_aux_stream, set, target, R);
     launch_sampler(m_aux_stream, key, sb);
     NGP_CUDA_CHECK(cudaEventRecord(m_ev_prefetch, m_aux_stream));
-    m_prefetch_key = key; m_prefetch_valid = true;
+    m_prefetch_key = key; m_prefetch_valid = true; m_prefetch_inflight = true;
+}
+
+// The same prefetch, enqueued from train_nerf_step(N) BEFORE the host has seen step N's counters: nerf_control_law (already on `s`, right
+// behind the loss kernel) leaves rays_per_batch / the inference size of step N+1 in device memory and the sampler kernels read them from
+// there; their grids are sized for the bounds.  train_end evaluates the same law on the host and adopts the result if it fits the bounds.
+void Testbed::launch_early_prefetch(cudaStream_t s, uint32_t target, uint32_t rays_bound, uint32_t samples_bound) {
+    (void)s;
+    const uint32_t set = (m_training_step + 1u) & 1u;      // m_training_step is still this step's; m_rng has already been advanced
+    static const bool after_mlp = [] { const char* e = getenv("NGP_PREFETCH_AFTER"); return e && std::string(e) == "mlp"; }();
+    NGP_CUDA_CHECK(cudaStreamWaitEvent(m_aux_stream, after_mlp ? m_ev_after_mlp : m_ev_after_loss, 0));
+    SamplerBuffers sb = sampler_buffers(m_aux_stream, set, target, rays_bound);
+    sb.dyn = m_step_params[set].as<StepParams>();
+    NGP_CUDA_CHECK(cudaMemsetAsync(sb.counters, 0, 32, m_aux_stream));
+    nerf_generate_training_samples(m_aux_stream, rays_bound, aabb, samples_bound, 0, m_rng, m_n_images, m_metas.as<ImageMeta>(), m_bitfield.as<uint8_t>(), m_max_cascade,
+                                   train_snap_to_pixel_centers, cone_angle_constant, 0, rays_bound, sb);
+    NGP_CUDA_CHECK(cudaEventRecord(m_ev_prefetch, m_aux_stream));
+    m_early_prefetch = true; m_early_rays_bound = rays_bound; m_early_samples_bound = samples_bound; m_prefetch_inflight = true;
+    m_early_dataset_version = m_dataset_version;
 }
 
 void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
@@ -461,6 +489,7 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
         NGP_CUDA_CHECK(cudaEventCreateWithFlags(&m_ev_counters, cudaEventDisableTiming));
         NGP_CUDA_CHECK(cudaEventCreateWithFlags(&m_ev_prefetch, cudaEventDisableTiming));
         NGP_CUDA_CHECK(cudaEventCreateWithFlags(&m_ev_after_mlp, cudaEventDisableTiming));
+        NGP_CUDA_CHECK(cudaEventCreateWithFlags(&m_ev_after_loss, cudaEventDisableTiming));
         NGP_CUDA_CHECK(cudaMallocHost(&m_host_counters, 8 * sizeof(uint32_t)));
         memset(m_host_counters, 0, 8 * sizeof(uint32_t));
     }
@@ -485,8 +514,8 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
 
     const SamplerKey key = sampler_key(R, max_inference, target);
     const bool prefetched = m_prefetch_valid && m_prefetch_key == key;
-    if (m_prefetch_valid) NGP_CUDA_CHECK(cudaStreamWaitEvent(s, m_ev_prefetch, 0));   // adopted or stale, it must have left the buffers
-    m_prefetch_valid = false;
+    if (m_prefetch_valid || m_prefetch_inflight) NGP_CUDA_CHECK(cudaStreamWaitEvent(s, m_ev_prefetch, 0));   // adopted or stale, it must have left the buffers
+    m_prefetch_valid = false; m_prefetch_inflight = false;
     if (prefetched) ++prefetch_hits; else launch_sampler(s, key, sb);
     NGP_CUDA_CHECK(cudaMemsetAsync(lb.loss, 0, sizeof(float) * R, s));
     const uint32_t ray_offset = m_rank * R, n_rays_global = m_world * R;
@@ -502,6 +531,21 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
     nerf_compute_loss(s, R, aabb, n_rays_total, m_rng, target, lc, m_n_images, m_metas.as<ImageMeta>(), m_mean.as<float>(), ray_offset, n_rays_global, sb, lb);
     NGP_CUDA_CHECK(cudaMemcpyAsync(m_host_counters, sb.counters, 16, cudaMemcpyDeviceToHost, s));   // read by train_end
     NGP_CUDA_CHECK(cudaEventRecord(m_ev_counters, s));
+    // device-side control law for the next step's sampler (single rank; data parallel keeps the host path: the law sees the rank mean)
+    uint32_t early_rays_bound = 0, early_samples_bound = 0;
+    {
+        const uint32_t next_step = m_training_step + 1u, skip = std::min(std::max(next_step / 16u, 1u), 16u);
+        const bool next_refreshes_grid = next_step % skip == 0;
+        const uint32_t rb = std::min<uint32_t>(1u << 18, (uint32_t)next_multiple((uint64_t)R + R / 2 + BATCH_GRANULARITY, BATCH_GRANULARITY));
+        const uint32_t lanes = sampler_lanes_per_ray ? sampler_lanes_per_ray : nerf_sampler_lanes_per_ray(rb);
+        if (device_control_law && prefetch_rays && m_all_images_u8 && !m_comm && m_world == 1 && !next_refreshes_grid && lanes != 1) {
+            early_rays_bound = rb;
+            early_samples_bound = std::min<uint32_t>(max_samples, (uint32_t)next_multiple((uint64_t)max_inference + max_inference / 2 + BATCH_GRANULARITY, BATCH_GRANULARITY));
+            StepParams* sp = m_step_params[next_step & 1u].get<StepParams>(1);
+            nerf_control_law(s, sb.counters, R, target, early_rays_bound, early_samples_bound, sp);
+            NGP_CUDA_CHECK(cudaEventRecord(m_ev_after_loss, s));
+        }
+    }
     if (m_comm) {   // global sample counts for the control law: summed while the backward pass runs
         uint32_t* dc = m_dp_counters.as<uint32_t>();
         NGP_CUDA_CHECK(cudaMemcpyAsync(dc, sb.counters + 1, 8, cudaMemcpyDeviceToDevice, s));   // [1] before compaction, [2] compacted
@@ -539,6 +583,7 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
     }
     m_trainer->grid_grads_clean = false;
     m_rng.advance();   // :4127
+    if (early_rays_bound) launch_early_prefetch(s, target, early_rays_bound, early_samples_bound);
 }
 
 // ---------------------------------------------------------------------------------------------------------------

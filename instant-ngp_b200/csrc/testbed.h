@@ -99,6 +99,9 @@ public:
     // generate the NEXT step's rays on a second stream while this step's backward pass and optimizer run (the walk depends on
     // the occupancy bitfield and the rng only, not on the weights); same samples either way, see launch_ray_prefetch()
     bool prefetch_rays = true;
+    // evaluate the rays_per_batch control law on the device as well and enqueue the next step's sampler before the host has read this
+    // step's counters (nerf_kernels.h StepParams); off: the sampler of step N+1 is launched by the host after it has read them.  Same results.
+    bool device_control_law = true;
     uint32_t prefetch_hits = 0;   // read-only: steps whose rays came from a prefetch
     // data parallel only: reduce-scatter the gradients, run Adam(+EMA) on this rank's 1/world of the entries, all-gather the fp16
     // parameters (instead of all-reduce + the full optimizer on every rank).  Same arithmetic per entry; the EMA (inference)
@@ -164,6 +167,10 @@ private:
     std::unique_ptr<Comm> m_comm; cudaStream_t m_comm_stream = nullptr; cudaEvent_t m_ev_slice = nullptr, m_ev_comm_done = nullptr, m_ev_dp_counters = nullptr;
     DeviceBuffer m_dp_counters;
     cudaStream_t m_copy_stream = nullptr; cudaEvent_t m_ev_copy_gate = nullptr, m_ev_copy_done = nullptr; bool m_copy_pending = false;
+    bool m_prefetch_inflight = false;     // a prefetch (adopted or not) may still be writing its buffer set: wait for m_ev_prefetch before reuse
+    bool m_early_prefetch = false; uint32_t m_early_rays_bound = 0, m_early_samples_bound = 0, m_early_dataset_version = 0;   // sampler of the next step enqueued from train_nerf_step
+    DeviceBuffer m_step_params[2]; cudaEvent_t m_ev_after_loss = nullptr;
+    void launch_early_prefetch(cudaStream_t s, uint32_t target, uint32_t rays_bound, uint32_t samples_bound);
     bool m_prefetch_valid = false, m_all_images_u8 = false; SamplerKey m_prefetch_key{}; uint32_t m_dataset_version = 0, m_last_set = 0;
     // image mode
     DeviceBuffer m_image; int m_image_w = 0, m_image_h = 0; DeviceBuffer m_img_pos, m_img_target, m_img_out, m_img_dl, m_img_loss;

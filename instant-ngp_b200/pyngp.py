@@ -53,7 +53,7 @@ def _stream():
 
 
 _BOOL_OPTS = {"random_bg_color", "linear_colors", "snap_to_pixel_centers", "train_snap_to_pixel_centers", "shall_train_encoding", "shall_train_network",
-              "image_snap_to_pixel_centers", "image_linear_colors", "image_stratified", "prefetch_rays", "dp_sharded_optimizer"}
+              "image_snap_to_pixel_centers", "image_linear_colors", "image_stratified", "prefetch_rays", "dp_sharded_optimizer", "device_control_law"}
 _FLOAT_OPTS = {"near_distance", "density_grid_decay", "render_min_transmittance", "cone_angle_constant"}
 _INT_OPTS = {"loss_type", "rgb_activation", "density_activation", "seed", "sampler_lanes_per_ray", "prefetch_hits"}
 
