@@ -470,13 +470,17 @@ def run_render(args):
         tb.train(args.batch)
     tb.sync_inference_params()
     torch.cuda.synchronize()
-    rows = [(r * H // world, (r + 1) * H // world) for r in range(world)]
-    y0, y1 = rows[rank]
+    # rows of rank r: every world-th row from r (default: equal work whatever the picture shows), or the contiguous band r (--render-bands)
+    if args.render_bands:
+        y0, y1, stride = rank * H // world, (rank + 1) * H // world, 1
+    else:
+        y0, y1, stride = rank, H, world
+    n_rows = len(range(y0, y1, stride))
     f = scene.focal_px(H)
-    band = torch.empty(y1 - y0, W, 4, dtype=torch.float32, device="cuda")
+    band = torch.empty(n_rows, W, 4, dtype=torch.float32, device="cuda")
     cam = views[7 % len(views)]["xform"]
     def frame():
-        tb.render(W, H, 1, camera_matrix=cam, focal_length=(f, f), y0=y0, y1=y1, out=band)
+        tb.render(W, H, 1, camera_matrix=cam, focal_length=(f, f), y0=y0, y1=y1, row_stride=stride, out=band)
     for _ in range(max(args.warmup, 2)):
         frame()
     def sync():
@@ -495,10 +499,15 @@ def run_render(args):
     # gather of the bands to rank 0 (equal band heights when world divides H)
     gather_ms = 0.0
     if world > 1:
-        full = [torch.empty_like(band) for _ in range(world)] if rank == 0 else None
+        max_rows = -(-H // world)
+        send = band if n_rows == max_rows else torch.cat([band, band.new_zeros(max_rows - n_rows, W, 4)])
+        full = [torch.empty_like(send) for _ in range(world)] if rank == 0 else None
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         for _ in range(2):
-            sync(); e0.record(); dist.gather(band, full, dst=0); e1.record(); sync()
+            sync(); e0.record(); dist.gather(send, full, dst=0)
+            if rank == 0:      # assemble the frame: bands stack, interleaved rows alternate
+                picture = (torch.cat(full) if args.render_bands else torch.stack(full, dim=1).reshape(max_rows * world, W, 4))[:H]
+            e1.record(); sync()
         gather_ms = e0.elapsed_time(e1)
     times.sort()
     cov = float((band[..., 3] > 0.5).float().mean())
@@ -506,7 +515,7 @@ def run_render(args):
         med = times[len(times) // 2]
         print(json.dumps({"metric": "nerf_render_ms_per_frame", "value": med, "unit": "ms/frame", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 2),
                           "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "f16 (fp32 accumulate)", "data": "synthetic",
-                          "config": {"workload": f"render_{W}x{H}_spp1_" + workload_name(args), "row_bands": world, "rows_per_rank": y1 - y0, "pretrain_steps_untimed": args.pretrain,
+                          "config": {"workload": f"render_{W}x{H}_spp1_" + workload_name(args), "row_sharding": "bands" if args.render_bands else "interleaved", "ranks": world, "rows_per_rank": n_rows, "pretrain_steps_untimed": args.pretrain,
                                      "parallelism": f"tiles{world}" if world > 1 else "single"},
                           "ms_min": times[0], "ms_max": times[-1], "Mpixels_per_s": W * H / med / 1e3, "gather_to_rank0_ms": gather_ms, "gather_bytes": W * H * 16,
                           "band0_coverage": cov}), flush=True)
@@ -531,6 +540,7 @@ def main():
                          "(profiles/r02_scaling.json)")
     ap.add_argument("--dense-allreduce", dest="sharded_optimizer", action="store_false", help="data parallel: one dense all-reduce + the full optimizer on every rank")
     ap.add_argument("--render", default="", help="WxH: time the inference render, rows sharded over the ranks (BASELINE config 5), instead of training")
+    ap.add_argument("--render-bands", action="store_true", help="--render: contiguous row bands per rank instead of interleaved rows")
     ap.add_argument("--repeats", type=int, default=15, help="K-step windows timed back to back; the median is reported")
     ap.add_argument("--cpu-steps", type=int, default=3, help="timed steps of the CPU arm (a full-batch step takes seconds)")
     args = ap.parse_args()

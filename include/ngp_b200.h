@@ -256,6 +256,24 @@ int ngp_testbed_density_grid(ngp_testbed_t t, int which, void** dev_ptr, uint64_
  * averaged over spp; camera = mat4x3 column major; out is a HOST buffer unless out_is_device */
 int ngp_testbed_render(ngp_testbed_t t, void* stream, const float* camera_matrix, const float* focal_length, const float* screen_center,
                        int32_t width, int32_t height, int32_t spp, int32_t y0, int32_t y1, float* rgba_out, int32_t out_is_device, float* depth_out);
+/* Testbed::render_to_cpu (python_api.cu:127-205 -> render_frame testbed.cu:4640-4760) headless, with the testbed's OWN view state
+ * (camera_matrix, fov / relative_focal_length, fov_axis, zoom, screen_center, render lens): spp samples are accumulated in "color_space"
+ * (accumulate_kernel, render_buffer.cu:232-260), then composited over "background_color" with "exposure", "tonemap_curve" and the output
+ * colour space (sRGB unless `linear`; tonemap_kernel, render_buffer.cu:533-565), then the ground-truth overlay of the selected training
+ * view when "render_ground_truth" is set (overlay_image_kernel, render_buffer.cu:348-418).  float32 RGBA rows [y0,y1) of a w x h frame
+ * into a HOST buffer unless out_is_device.  Camera-path arguments of the reference (start_t / end_t / fps / shutter_fraction) belong to
+ * the GUI's camera path, which is out of scope: the binding rejects them. */
+int ngp_testbed_render_frame(ngp_testbed_t t, void* stream, int32_t width, int32_t height, int32_t spp, int32_t linear, int32_t y0, int32_t y1,
+                             void* rgba_out, int32_t out_is_device);
+/* Testbed::reset_camera (testbed.cu:858-884), set_nerf_camera_matrix (:789-791; mat4x3 column major in the NeRF convention),
+ * set_camera_to_training_view (:841-856: pose, focal length, principal point and lens of training view i become the view state) */
+int ngp_testbed_reset_camera(ngp_testbed_t t);
+int ngp_testbed_set_nerf_camera_matrix(ngp_testbed_t t, const float* nerf_camera_to_world_12);
+int ngp_testbed_set_camera_to_training_view(ngp_testbed_t t, int32_t trainview);
+/* vector-valued members (python_api.cu:452-537): "camera_matrix" (12, mat4x3 column major, NGP convention), "screen_center" (2),
+ * "relative_focal_length" (2), "up_dir" (3), "background_color" (4, sRGB RGBA), "aabb" / "render_aabb" (6: min xyz, max xyz) */
+int ngp_testbed_set_vector(ngp_testbed_t t, const char* name, const float* values, uint32_t count);
+int ngp_testbed_get_vector(ngp_testbed_t t, const char* name, float* values, uint32_t count);
 /* nerf.render_lens / render_with_lens_distortion (set_camera_to_training_view): lens model applied to the rays of
  * ngp_testbed_render; lens_mode 0 Perspective, 1 OpenCV (k1, k2, p1, p2) */
 int ngp_testbed_set_render_lens(ngp_testbed_t t, int32_t lens_mode, const float* lens_params4);
@@ -269,7 +287,12 @@ int ngp_testbed_compute_image_mse(ngp_testbed_t t, void* stream, int32_t quantiz
  * "snap_to_pixel_centers" (bool, default 0: Testbed::m_snap_to_pixel_centers, render rays: pixel offset of sample 0 for every sample),
  * "near_distance","density_grid_decay","render_min_transmittance","cone_angle_constant" (float),
  * "loss_type","rgb_activation","density_activation" (enum), "seed" (integer), "image_snap_to_pixel_centers",
- * "image_linear_colors","image_stratified" (bool), "background_r/g/b" (float),
+ * "image_linear_colors","image_stratified" (bool), "background_r/g/b/a" (float),
+ * view + output stage: "fov" (degrees along fov_axis), "fov_axis" (0|1), "zoom", "scale", "exposure" (stops), "color_space"
+ * (0 Linear | 1 SRGB | 2 VisPosNeg), "tonemap_curve" (0 Identity | 1 ACES | 2 Hable | 3 Reinhard), "render_mode" (ERenderMode: 0 AO,
+ * 1 Shade, 3 Positions, 4 Depth, 6 Cost, 9 EncodingVis; 2 Normals is rejected), "render_ground_truth" (bool), "ground_truth_alpha",
+ * "training_view", "render_with_lens_distortion" (bool), "render_near_distance",
+ * "render_row_stride" (default 1; both render entry points then produce rows y0, y0 + stride, ... < y1: interleaved tile sharding),
  * "sampler_lanes_per_ray" (0 automatic | 1 | 2 | 4 | 8 | 32: lanes that cooperate on one training ray; results are identical),
  * "prefetch_rays" (bool, default 1: the next step's rays are generated on a second stream beside this step's backward pass
  * and optimizer whenever the next step does not refresh the occupancy grid first; results are identical),

@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libngp_b200.so")
+LIB_PATH = os.environ.get("NGP_B200_LIB") or os.path.join(_HERE, "libngp_b200.so")   # NGP_B200_LIB: A/B timing builds (csrc/Makefile target `ab`)
 
 _lib = None
 
@@ -126,6 +126,12 @@ SYMBOLS = {
     "ngp_testbed_density_grid": (i32, [vp, i32, C.POINTER(vp), C.POINTER(u64)]),
     "ngp_testbed_render": (i32, [vp, vp, vp, vp, vp, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, vp, C.c_int32, vp]),
     "ngp_testbed_set_render_lens": (i32, [vp, C.c_int32, vp]),
+    "ngp_testbed_render_frame": (i32, [vp, vp, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, vp, C.c_int32]),
+    "ngp_testbed_reset_camera": (i32, [vp]),
+    "ngp_testbed_set_nerf_camera_matrix": (i32, [vp, vp]),
+    "ngp_testbed_set_camera_to_training_view": (i32, [vp, C.c_int32]),
+    "ngp_testbed_set_vector": (i32, [vp, cp, vp, u32]),
+    "ngp_testbed_get_vector": (i32, [vp, cp, vp, u32]),
     "ngp_testbed_training_view": (i32, [vp, u32, C.POINTER(TrainingImage)]),
     "ngp_testbed_n_training_views": (u32, [vp]),
     "ngp_testbed_compute_image_mse": (i32, [vp, vp, C.c_int32, C.POINTER(f32)]),

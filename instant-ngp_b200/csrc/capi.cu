@@ -266,6 +266,7 @@ int ngp_testbed_load_nerf_dataset(ngp_testbed_t t, void* stream, ngp_nerf_datase
     static_assert(sizeof(ngp_training_image) == sizeof(HostImage), "ABI struct drift");
     t->tb.set_nerf_dataset(S(stream), (uint32_t)views.size(), reinterpret_cast<const HostImage*>(views.data()), d->ds.aabb_scale);
     t->tb.set_dataset_scale_offset(d->ds.scale, d->ds.offset);
+    t->tb.apply_dataset_view_hints(d->ds.has_render_aabb, d->ds.render_aabb, d->ds.up);
     NGP_API_END
 }
 int ngp_testbed_set_training_image(ngp_testbed_t t, void* stream, uint32_t frame_idx, const void* pixels_host) {
@@ -396,6 +397,33 @@ int ngp_testbed_render(ngp_testbed_t t, void* stream, const float* cam, const fl
     t->tb.render(S(stream), cam, focal, center, w, h, spp, y0, y1, out, out_is_device != 0, depth);
     NGP_API_END
 }
+int ngp_testbed_render_frame(ngp_testbed_t t, void* stream, int32_t w, int32_t h, int32_t spp, int32_t linear, int32_t y0, int32_t y1, void* out, int32_t out_is_device) {
+    NGP_API_BEGIN require_device(); NGP_CHECK(t && out, "null argument");
+    t->tb.render_frame(S(stream), w, h, spp, linear == 0, y0, y1, reinterpret_cast<float*>(out), out_is_device != 0);
+    NGP_API_END
+}
+int ngp_testbed_reset_camera(ngp_testbed_t t) { NGP_API_BEGIN NGP_CHECK(t, "null argument"); t->tb.reset_camera(); NGP_API_END }
+int ngp_testbed_set_nerf_camera_matrix(ngp_testbed_t t, const float* m) { NGP_API_BEGIN NGP_CHECK(t && m, "null argument"); t->tb.set_nerf_camera_matrix(m); NGP_API_END }
+int ngp_testbed_set_camera_to_training_view(ngp_testbed_t t, int32_t v) { NGP_API_BEGIN NGP_CHECK(t, "null argument"); t->tb.set_camera_to_training_view(v); NGP_API_END }
+namespace {
+float* vector_field(ngp::Testbed& tb, const std::string& n, uint32_t count) {
+    struct E { const char* name; float* p; uint32_t n; };
+    const E table[] = {{"camera_matrix", tb.camera, 12}, {"screen_center", tb.screen_center, 2}, {"relative_focal_length", tb.relative_focal_length, 2},
+                       {"up_dir", tb.up_dir, 3}, {"background_color", tb.background_color, 4}, {"aabb", tb.aabb.min, 6}, {"render_aabb", tb.render_aabb.min, 6}};
+    for (const E& e : table) if (n == e.name) { NGP_CHECK(count == e.n, "vector option '" + n + "' has " + std::to_string(e.n) + " components"); return e.p; }
+    throw ngp::Error("unknown vector option '" + n + "'");
+}
+}
+int ngp_testbed_set_vector(ngp_testbed_t t, const char* name, const float* v, uint32_t count) {
+    NGP_API_BEGIN NGP_CHECK(t && name && v, "null argument");
+    memcpy(vector_field(t->tb, name, count), v, count * sizeof(float));
+    NGP_API_END
+}
+int ngp_testbed_get_vector(ngp_testbed_t t, const char* name, float* v, uint32_t count) {
+    NGP_API_BEGIN NGP_CHECK(t && name && v, "null argument");
+    memcpy(v, vector_field(t->tb, name, count), count * sizeof(float));
+    NGP_API_END
+}
 int ngp_testbed_set_render_lens(ngp_testbed_t t, int32_t lens_mode, const float* p) {
     NGP_API_BEGIN NGP_CHECK(t, "null argument");
     NGP_CHECK(lens_mode == LENS_PERSPECTIVE || (lens_mode == LENS_OPENCV && p), "render lens must be Perspective (0) or OpenCV (1) with 4 parameters");
@@ -428,7 +456,9 @@ int ngp_testbed_debug_buffer(ngp_testbed_t t, const char* name, void** ptr, uint
     X(random_bg_color, bool) X(linear_colors, bool) X(snap_to_pixel_centers, bool) X(train_snap_to_pixel_centers, bool) X(shall_train_encoding, bool) X(shall_train_network, bool) \
     X(near_distance, float) X(density_grid_decay, float) X(render_min_transmittance, float) X(cone_angle_constant, float)         \
     X(loss_type, int) X(rgb_activation, int) X(density_activation, int) X(seed, uint64_t)                                        \
-    X(image_snap_to_pixel_centers, bool) X(image_linear_colors, bool) X(image_stratified, bool) X(sampler_lanes_per_ray, uint32_t) X(prefetch_rays, bool) X(prefetch_hits, uint32_t) X(dp_sharded_optimizer, bool) X(device_control_law, bool)
+    X(image_snap_to_pixel_centers, bool) X(image_linear_colors, bool) X(image_random_mode, int) X(sampler_lanes_per_ray, uint32_t) X(prefetch_rays, bool) X(prefetch_hits, uint32_t) X(dp_sharded_optimizer, bool) X(device_control_law, bool) \
+    X(exposure, float) X(zoom, float) X(scale, float) X(ground_truth_alpha, float) X(render_near_distance, float) X(fov_axis, int) X(training_view, int)                      \
+    X(color_space, int) X(tonemap_curve, int) X(render_mode, int) X(render_ground_truth, bool) X(render_with_lens_distortion, bool) X(render_row_stride, int)
 
 int ngp_testbed_set_option(ngp_testbed_t t, const char* name, double value) {
     NGP_API_BEGIN NGP_CHECK(t && name, "null argument");
@@ -439,6 +469,9 @@ int ngp_testbed_set_option(ngp_testbed_t t, const char* name, double value) {
     if (n == "background_r") { t->tb.background_color[0] = (float)value; return 0; }
     if (n == "background_g") { t->tb.background_color[1] = (float)value; return 0; }
     if (n == "background_b") { t->tb.background_color[2] = (float)value; return 0; }
+    if (n == "background_a") { t->tb.background_color[3] = (float)value; return 0; }
+    if (n == "fov") { t->tb.set_fov((float)value); return 0; }
+    if (n == "image_stratified") { t->tb.image_random_mode = value != 0 ? IMG_RANDOM_STRATIFIED : IMG_RANDOM_RANDOM; return 0; }   // round-1 name
     throw Error("unknown option '" + n + "'");
     NGP_API_END
 }
@@ -451,6 +484,9 @@ int ngp_testbed_get_option(ngp_testbed_t t, const char* name, double* value) {
     if (n == "background_r") { *value = t->tb.background_color[0]; return 0; }
     if (n == "background_g") { *value = t->tb.background_color[1]; return 0; }
     if (n == "background_b") { *value = t->tb.background_color[2]; return 0; }
+    if (n == "background_a") { *value = t->tb.background_color[3]; return 0; }
+    if (n == "fov") { *value = t->tb.fov(); return 0; }
+    if (n == "image_stratified") { *value = t->tb.image_random_mode == IMG_RANDOM_STRATIFIED; return 0; }
     if (n == "l2_window_bytes") { *value = t->tb.trainer() ? (double)t->tb.trainer()->l2_window_bytes : 0.0; return 0; }   // read-only
     throw Error("unknown option '" + n + "'");
     NGP_API_END

@@ -145,10 +145,12 @@ struct LevelCorners {
 // 16-byte stores fill four whole 128-byte core matrices of the blk8 output.
 template <uint32_t D, uint32_t F>
 __global__ void __launch_bounds__(256) grid_forward_kernel(const GridLayout g, const __half* __restrict__ table, const float* __restrict__ x,
-                                                           uint32_t x_stride, uint32_t n, __half* __restrict__ y, int y_layout) {
+                                                           uint32_t x_stride, uint32_t n, __half* __restrict__ y, int y_layout,
+                                                           const uint32_t* __restrict__ n_dyn) {
     constexpr uint32_t LPC = 8 / F;          // levels per 8-feature chunk
     constexpr uint32_t NC = 1u << D;
     const uint32_t row = blockIdx.x * blockDim.x + threadIdx.x, chunk = blockIdx.y;
+    if (n_dyn) n = min(n, __ldg(n_dyn));
     if (row >= n) return;
     const float* xp = x + (size_t)row * x_stride;
     float xs[D];
@@ -408,11 +410,11 @@ __global__ void grid_init_kernel(uint64_t n, Pcg32 rng, float* __restrict__ p) {
     } while (0)
 
 void grid_forward(cudaStream_t s, const GridLayout& g, const __half* table, const float* x, uint32_t x_stride, uint32_t n,
-                  __half* y, int y_layout) {
+                  __half* y, int y_layout, const uint32_t* n_dyn) {
     if (n == 0) return;
     NGP_PROFILE_SCOPE(s, "grid_forward", n);
     const dim3 blocks(div_round_up(n, 256), g.padded_width / 8, 1);
-    GRID_DISPATCH(grid_forward_kernel, g, table, x, x_stride, n, y, y_layout);
+    GRID_DISPATCH(grid_forward_kernel, g, table, x, x_stride, n, y, y_layout, n_dyn);
 }
 
 // runs per warp up to which a level is aggregated (0 = never); NGP_AGG_MAX_RUNS overrides for experiments.  Measured (tools/sweep_agg.sh,

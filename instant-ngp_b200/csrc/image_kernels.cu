@@ -2,10 +2,11 @@
 // :440-463 image_coords_from_idx / image_mse_kernel) and the tcnn L2 loss used by Trainer::training_step
 // (testbed_image.cu:276).  Sample generation, stratification and target lookup are fused into one kernel.
 #include "image_kernels.h"
+#include "nerf_device.cuh"
 
 namespace ngp {
 
-NGP_D float lin2srgb(float l) { return l < 0.0031308f ? 12.92f * l : 1.055f * powf(l, 0.41666f) - 0.055f; }
+NGP_D float lin2srgb(float l) { return linear_to_srgb(l); }
 
 NGP_D void image_lookup(const float* __restrict__ image, int W, int H, float& px, float& py, bool snap, bool linear_colors, float* v) {
     auto read_val = [&](int x, int y, float* o) {
@@ -27,13 +28,23 @@ NGP_D void image_lookup(const float* __restrict__ image, int W, int H, float& px
     }
 }
 
-// positions: element e of the [n][2] array is float #e of the pcg32 stream (generate_random_uniform), then stratify2_kernel
-__global__ void image_batch_kernel(uint32_t n, Pcg32 rng, uint32_t log2_batch, bool stratify, const float* __restrict__ image, int W, int H, bool snap,
-                                   bool linear_colors, float* __restrict__ pos, float* __restrict__ target) {
+// halton<base>(idx) (random_val.cuh:293-305): radical inverse, accumulated in float exactly as the reference does
+template <uint32_t BASE> NGP_D float halton(size_t idx) {
+    float f = 1, result = 0;
+    while (idx > 0) { f /= BASE; result += f * (float)(idx % BASE); idx /= BASE; }
+    return result;
+}
+
+// positions by image.random_mode (testbed_image.cu:227-245): Halton -> halton23_kernel (:41-46), Sobol -> sobol2_kernel (:48-53, Owen-scrambled,
+// seeded), otherwise element e of the [n][2] array is float #e of the pcg32 stream (generate_random_uniform), then stratify2_kernel (:62-76)
+__global__ void image_batch_kernel(uint32_t n, Pcg32 rng, int random_mode, size_t base_idx, uint32_t seed, uint32_t log2_batch, bool stratify,
+                                   const float* __restrict__ image, int W, int H, bool snap, bool linear_colors, float* __restrict__ pos, float* __restrict__ target) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    rng.advance((int64_t)((uint64_t)i * 2));
-    float px = rng.next_float(), py = rng.next_float();
+    float px, py;
+    if (random_mode == IMG_RANDOM_HALTON) { px = halton<2>(base_idx + i); py = halton<3>(base_idx + i); }
+    else if (random_mode == IMG_RANDOM_SOBOL) { float v[2]; ld_random_val_2d((uint32_t)(base_idx + i), seed, v); px = v[0]; py = v[1]; }
+    else { rng.advance((int64_t)((uint64_t)i * 2)); px = rng.next_float(); py = rng.next_float(); }
     if (stratify) {
         const uint32_t log2s = log2_batch / 2, size = 1u << log2s;
         const uint32_t ib = i & ((1u << log2_batch) - 1), x = ib & (size - 1), y = ib >> log2s;
@@ -71,10 +82,11 @@ __global__ void image_se_kernel(uint32_t n, const float* __restrict__ target, co
     se[i] = acc / 3.0f;
 }
 
-void image_generate_batch(cudaStream_t s, uint32_t n, Pcg32 rng, bool stratify, const float* image, int W, int H, bool snap, bool linear_colors, float* pos, float* target) {
+void image_generate_batch(cudaStream_t s, uint32_t n, Pcg32 rng, int random_mode, size_t base_idx, uint32_t seed, const float* image, int W, int H, bool snap,
+                          bool linear_colors, float* pos, float* target) {
     uint32_t log2n = 0; while ((1u << log2n) < n) ++log2n;
-    const bool can_stratify = stratify && (1u << log2n) == n && (log2n % 2 == 0);
-    image_batch_kernel<<<div_round_up(n, 256), 256, 0, s>>>(n, rng, log2n, can_stratify, image, W, H, snap, linear_colors, pos, target);
+    const bool can_stratify = random_mode == IMG_RANDOM_STRATIFIED && (1u << log2n) == n && (log2n % 2 == 0);
+    image_batch_kernel<<<div_round_up(n, 256), 256, 0, s>>>(n, rng, random_mode, base_idx, seed, log2n, can_stratify, image, W, H, snap, linear_colors, pos, target);
     NGP_POST_LAUNCH();
 }
 void image_eval_coords(cudaStream_t s, uint32_t n, uint32_t offset, const float* image, int W, int H, bool linear_colors, float* pos, float* target) {

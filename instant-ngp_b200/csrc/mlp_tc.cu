@@ -137,6 +137,7 @@ struct FwdParams {
     const float* coords;      // [n][7] (MODE_NERF)
     __half* out; uint32_t out_stride;
     uint32_t n_tiles;
+    const uint32_t* n_dyn;    // optional device-side row count: tiles beyond ceil(*n_dyn / 128) are skipped (n_tiles sizes the grid)
     long long* probe;         // debug (NGP_MLP_PROBE=1): per-phase clock64 deltas of CTA 0 / thread 0, summed over its tiles; null in normal runs
 };
 
@@ -190,13 +191,15 @@ __global__ void __launch_bounds__(128) mlp_forward_kernel(const FwdParams p) {
     __half* r0 = reinterpret_cast<__half*>(smem + L.r0);
     constexpr uint32_t X_BYTES = TILE_ROWS * PW * 2;
 
+    // n_dyn: the row count lives in device memory (tracer: rays alive x steps, known only after the compaction kernel has run)
+    const uint32_t n_tiles = p.n_dyn ? min(p.n_tiles, (__ldg(p.n_dyn) + TILE_ROWS - 1) / TILE_ROWS) : p.n_tiles;
     StageSync stage{bar_mma, 0};
     uint32_t full_parity = 0;
-    if (tid == 0 && blockIdx.x < p.n_tiles) {
+    if (tid == 0 && blockIdx.x < n_tiles) {
         mbar_expect_tx(&bar_full[0], X_BYTES);
         bulk_g2s(smem + L.x0, p.enc + (size_t)blockIdx.x * TILE_ROWS * PW, X_BYTES, &bar_full[0]);
     }
-    for (uint32_t tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+    for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const uint32_t next = tile + gridDim.x;
         const uint32_t row_g = tile * TILE_ROWS + tid;
         float dir[3] = {0.f, 0.f, 0.f};
@@ -206,7 +209,7 @@ __global__ void __launch_bounds__(128) mlp_forward_kernel(const FwdParams p) {
         // ---- density / plain network ----
         stage.run([&] { gemm_act_wT<64>(tmem_base, X0, 0, Operand{sbase + L.wd[0], PW}, PW); });
         // the first layer's MMAs have completed: the input tile is free -> fetch the next one under the remaining layers
-        if (tid == 0 && next < p.n_tiles) {
+        if (tid == 0 && next < n_tiles) {
             mbar_expect_tx(&bar_full[0], X_BYTES);
             bulk_g2s(smem + L.x0, p.enc + (size_t)next * TILE_ROWS * PW, X_BYTES, &bar_full[0]);
         }
@@ -336,16 +339,18 @@ __global__ void __launch_bounds__(128) mlp_forward_ts_kernel(const FwdParams p) 
     const Operand X0 = {sbase + L.x0, PW};
     constexpr uint32_t X_BYTES = TILE_ROWS * PW * 2;
 
+    // n_dyn: the row count lives in device memory (tracer: rays alive x steps, known only after the compaction kernel has run)
+    const uint32_t n_tiles = p.n_dyn ? min(p.n_tiles, (__ldg(p.n_dyn) + TILE_ROWS - 1) / TILE_ROWS) : p.n_tiles;
     StageTs stage{bar_mma, 0};
     uint32_t full_parity = 0;
-    if (tid == 0 && blockIdx.x < p.n_tiles) {
+    if (tid == 0 && blockIdx.x < n_tiles) {
         mbar_expect_tx(bar_full, X_BYTES);
         bulk_g2s(smem + L.x0, p.enc + (size_t)blockIdx.x * TILE_ROWS * PW, X_BYTES, bar_full);
     }
     const bool probing = p.probe != nullptr && blockIdx.x == 0 && tid == 0;
     long long tp = 0; uint32_t ph = 0;
 #define PROBE() do { if (probing) { const long long now = clock64(); p.probe[ph++] += now - tp; tp = now; } } while (0)
-    for (uint32_t tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+    for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         if (probing) { tp = clock64(); ph = 0; p.probe[15] += 1; }
         const uint32_t next = tile + gridDim.x;
         const uint32_t row_g = tile * TILE_ROWS + tid;
@@ -360,7 +365,7 @@ __global__ void __launch_bounds__(128) mlp_forward_ts_kernel(const FwdParams p) 
 
         // ---- density / plain network: first layer reads the TMA-delivered input tile from shared memory ----
         stage.run([&] { gemm_act_wT<64>(acc, X0, 0, Operand{sbase + L.wd[0], PW}, PW); });
-        if (tid == 0 && next < p.n_tiles) {   // the input tile is free: fetch the next one under the remaining layers
+        if (tid == 0 && next < n_tiles) {   // the input tile is free: fetch the next one under the remaining layers
             mbar_expect_tx(bar_full, X_BYTES);
             bulk_g2s(smem + L.x0, p.enc + (size_t)next * TILE_ROWS * PW, X_BYTES, bar_full);
         }
@@ -785,17 +790,17 @@ static uint32_t tiles_of(uint32_t n) {
 }
 
 void nerf_mlp_forward(cudaStream_t s, const NerfNetDims& d, const __half* wd, const __half* wr, const __half* enc, const float* coords,
-                      uint32_t n, __half* out) {
+                      uint32_t n, __half* out, const uint32_t* n_dyn) {
     if (n == 0) return;
     NGP_PROFILE_SCOPE(s, "nerf_mlp_forward", n);
-    FwdParams p{wd, wr, enc, coords, out, 4, tiles_of(n), nullptr};
+    FwdParams p{wd, wr, enc, coords, out, 4, tiles_of(n), n_dyn, nullptr};
     NERF_DISPATCH(launch_fwd, MODE_NERF, d, s, p);
 }
 
 void nerf_mlp_density(cudaStream_t s, const NerfNetDims& d, const __half* wd, const __half* enc, uint32_t n, __half* out) {
     if (n == 0) return;
     NGP_PROFILE_SCOPE(s, "nerf_mlp_density", n);
-    FwdParams p{wd, nullptr, enc, nullptr, out, 1, tiles_of(n), nullptr};
+    FwdParams p{wd, nullptr, enc, nullptr, out, 1, tiles_of(n), nullptr, nullptr};
     NerfNetDims dd = d; dd.rgb_hidden = 1;
     NERF_DISPATCH(launch_fwd, MODE_DENSITY, dd, s, p);
 }
@@ -812,7 +817,7 @@ void mlp_forward(cudaStream_t s, uint32_t in_w, uint32_t nh, const __half* w, co
     if (n == 0) return;
     NGP_CHECK(out_stride % 8 == 0 && out_stride >= 16, "mlp_forward: out_stride must be a multiple of 8 and >= 16");
     NGP_PROFILE_SCOPE(s, "mlp_forward", n);
-    FwdParams p{w, nullptr, in, nullptr, out, out_stride, tiles_of(n), nullptr};
+    FwdParams p{w, nullptr, in, nullptr, out, out_stride, tiles_of(n), nullptr, nullptr};
     PLAIN_DISPATCH(launch_fwd, in_w, nh, s, p);
 }
 

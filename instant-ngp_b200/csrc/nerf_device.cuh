@@ -50,14 +50,33 @@ NGP_HD float div_by_stepsize(float t) {
     return t / S;
 }
 
+// the same for either sign: round-to-nearest division and every operation of the refinement are odd in t
+NGP_HD float div_by_stepsize_signed(float t) {
+    constexpr float S = SQRT3 / (float)NERF_STEPS, RS = 1.0f / S;
+    const float at = fabsf(t);
+    if (at >= 1e-30f && at < 2048.0f) { const float q = t * RS; return fmaf(fmaf(-q, S, t), RS, q); }
+    return t / S;
+}
+
 // The same three functions with everything that depends on the cone angle alone evaluated once (the reference recomputes
 // log1p_c, a, b, at, bt — six logf and two expf — inside every call; per marcher step that is ~20 transcendentals on the
 // serial t chain).  Same expressions on the same inputs, hence the same bits; what is left per call is one logf or one expf.
+//
+// The division logf(t) / log1p_c of the logarithmic regime sits on the marcher's serial chain three times per skipped voxel.  For the
+// cone angle every aabb_scale > 1 scene uses (1/256, testbed_nerf.cu:3109: log1p_c = 0x3b7f8055) the quotient q = x * (1/L) refined by one
+// exact-residual FMA step equals the IEEE quotient x / L for EVERY float x with 1e-30 <= |x| < 8 (tools/verify_fast_div_log1p.c, exhaustive:
+// 1 723 562 816 values, 0 mismatches; logf(t) lies in [-0.84, 6.1] over the whole regime), so that form is used there — 3 dependent
+// operations instead of the ~8-deep IEEE division sequence.  Any other cone angle, and x outside the verified range, divides.
+constexpr uint32_t LOG1P_C_VERIFIED_BITS = 0x3b7f8055u;   // ngp_logf(1 + 1/256)
 struct Cone {
-    float angle, log1p_c, a, b, at, bt;
-    NGP_HD explicit Cone(float cone_angle) : angle(cone_angle), log1p_c(0.f), a(0.f), b(0.f), at(0.f), bt(0.f) {
+    float angle, log1p_c, a, b, at, bt, rl; bool fast_div;
+    NGP_HD explicit Cone(float cone_angle) : angle(cone_angle), log1p_c(0.f), a(0.f), b(0.f), at(0.f), bt(0.f), rl(0.f), fast_div(false) {
         if (cone_angle <= 1e-5f) return;
         log1p_c = ngp_logf(1.0f + cone_angle);
+        rl = 1.0f / log1p_c; fast_div = ngp_f2u(log1p_c) == LOG1P_C_VERIFIED_BITS;
+#ifdef NGP_AB_OLD_MATH
+        fast_div = false;
+#endif
         a = (ngp_logf(MIN_CONE_STEPSIZE()) - ngp_logf(log1p_c)) / log1p_c;
         b = (ngp_logf(MAX_CONE_STEPSIZE()) - ngp_logf(log1p_c)) / log1p_c;
         at = ngp_expf(a * log1p_c); bt = ngp_expf(b * log1p_c);
@@ -65,8 +84,12 @@ struct Cone {
 };
 NGP_HD float to_stepping_space(float t, const Cone& c) {
     if (c.angle <= 1e-5f) return div_by_stepsize(t);   // == t / MIN_CONE_STEPSIZE(), bit for bit
-    if (t <= c.at) return (t - c.at) / MIN_CONE_STEPSIZE() + c.a;
-    else if (t <= c.bt) return ngp_logf(t) / c.log1p_c;
+    if (t <= c.at) return div_by_stepsize_signed(t - c.at) + c.a;   // == (t - at) / MIN_CONE_STEPSIZE() + a
+    else if (t <= c.bt) {
+        const float x = ngp_logf(t), ax = fabsf(x);
+        if (c.fast_div && ax >= 1e-30f && ax < 8.0f) { const float q = x * c.rl; return fmaf(fmaf(-q, c.log1p_c, x), c.rl, q); }
+        return x / c.log1p_c;
+    }
     else return (t - c.bt) / MAX_CONE_STEPSIZE() + c.b;
 }
 NGP_HD float from_stepping_space(float n, const Cone& c) {

@@ -1231,28 +1231,45 @@ void nerf_fill_rollover(cudaStream_t s, uint32_t n_target, const uint32_t* n_inp
 // compact_kernel_nerf (:2198-2226), generate_next_nerf_network_inputs (:948-1022), composite_kernel_nerf (:1024-1230,
 // Shade mode only), shade_kernel_nerf (:2164-2196).
 // =================================================================================================================
-NGP_D float advance_to_occupied(float t, const Cone& cone, V3 o, V3 d, V3 idir, const uint8_t* __restrict__ bitfield, uint32_t min_mip, uint32_t max_mip, const Aabb& aabb) {
+// coarse bit of the 32^3 cell that holds pos (unit cube only; positions outside clamp to the border cell, whose dilated bit covers them)
+NGP_D bool coarse_bit_at(const uint32_t* __restrict__ coarse, V3 p) {
+    const uint32_t x = (uint32_t)clampi((int)floorf(p.x * COARSE_RES), 0, COARSE_RES - 1), y = (uint32_t)clampi((int)floorf(p.y * COARSE_RES), 0, COARSE_RES - 1),
+                   z = (uint32_t)clampi((int)floorf(p.z * COARSE_RES), 0, COARSE_RES - 1);
+    const uint32_t c = (z * COARSE_RES + y) * COARSE_RES + x;
+    return (__ldg(coarse + (c >> 5)) >> (c & 31u)) & 1u;
+}
+// occupancy look-up of the tracer.  With the coarse table (max_mip == 0, walk inside the unit cube) a clear coarse bit answers "empty"
+// from the 4 KB table in L1 instead of the 2 MB bitfield in L2: the dilated coarse cell is clear only if every fine cell in and around
+// it is, so the answer is the bitfield's.
+NGP_D bool tracer_occupied(V3 pos, const uint8_t* __restrict__ bitfield, uint32_t mip, const uint32_t* __restrict__ coarse) {
+    if (coarse && !coarse_bit_at(coarse, pos)) return false;
+    return density_grid_occupied_at(pos, bitfield, mip);
+}
+NGP_D float advance_to_occupied(float t, const Cone& cone, V3 o, V3 d, V3 idir, const uint8_t* __restrict__ bitfield, uint32_t min_mip, uint32_t max_mip, const Aabb& aabb,
+                                const uint32_t* __restrict__ coarse = nullptr) {
     while (true) {   // if_unoccupied_advance_to_next_occupied_voxel (:811-845)
         const V3 pos = ray_at(o, d, t);
         if (t >= MAX_DEPTH || !aabb_contains(aabb, pos)) return MAX_DEPTH;
         uint32_t mip = (uint32_t)clampi((int)mip_from_pos(pos, NERF_CASCADES - 1), (int)min_mip, (int)max_mip);
-        if (!bitfield || density_grid_occupied_at(pos, bitfield, mip)) return t;
+        if (!bitfield || tracer_occupied(pos, bitfield, mip, coarse)) return t;
         while (mip < max_mip && !density_grid_occupied_at(pos, bitfield, mip + 1)) ++mip;
         t = advance_to_next_voxel(t, cone, pos, d, idir, mip);
     }
 }
 
 __global__ void init_rays_kernel(RenderCamera cam, uint32_t sample_index, bool snap, Aabb render_aabb, const uint8_t* __restrict__ bitfield,
-                                 uint32_t max_mip, float cone_angle, RaysSoa rays, float* __restrict__ frame_rgba, float* __restrict__ frame_depth) {
+                                 uint32_t max_mip, float cone_angle, RaysSoa rays, float* __restrict__ frame_rgba, float* __restrict__ frame_depth, float near_distance,
+                                 const uint32_t* __restrict__ coarse) {
     const Cone cone(cone_angle);
     const uint32_t x = threadIdx.x + blockDim.x * blockIdx.x, yl = threadIdx.y + blockDim.y * blockIdx.y;
-    const uint32_t W = cam.res[0], y = cam.y0 + yl;
+    const uint32_t W = cam.res[0], y = cam.y0 + yl * (uint32_t)cam.y_stride;
     if (x >= W || y >= (uint32_t)cam.y1) return;
     const uint32_t local = x + W * yl, idx = x + W * y;
     float off[2]; ld_random_pixel_offset(snap ? 0 : sample_index, off);
     const float u = ((float)x + off[0]) / (float)W, v = ((float)y + off[1]) / (float)cam.res[1];
     V3 o, d;
     uv_to_ray(cam.camera, cam.res, cam.focal_length, cam.screen_center, cam.lens_mode, cam.lens_params, u, v, o, d);
+    if (near_distance != 0.f) o = ray_at(o, d, near_distance);   // uv_to_ray: origin += dir * near_distance (dir not yet normalised)
     NerfPayload& p = rays.payload[local];
     p.max_weight = 0.0f; p.idx = idx; p.n_steps = 0; p.alive = 0; p.pad = 0;
     p.origin[0] = o.x; p.origin[1] = o.y; p.origin[2] = o.z;
@@ -1266,23 +1283,39 @@ __global__ void init_rays_kernel(RenderCamera cam, uint32_t sample_index, bool s
     float t = fmaxf(tmin, 0.0f) + 1e-6f;
     p.t = t;
     if (!aabb_contains(render_aabb, ray_at(o, d, t))) return;
+    // Four fifths of the pixels of a typical frame see nothing.  The exact walk would still follow each of those rays through ~160 empty
+    // voxels, one dependent look-up per voxel; the conservative coarse test (see ray_touches_coarse) proves "no occupied cell on the ray"
+    // from ~35 look-ups in a 4 KB table instead, and the ray ends up exactly as the walk would leave it: not alive, t at the aabb entry.
+    if (coarse && !ray_touches_coarse(coarse, o, d, fmaxf(tmin, 0.0f), tmax, 0, 1)) return;
     // advance_pos_nerf: jittered first step, then skip to the first occupied voxel
     const V3 idir = v3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
     t = advance_n_steps(t, cone, ld_random_val(sample_index, idx * 786433u));
-    t = advance_to_occupied(t, cone, o, d, idir, bitfield, 0, max_mip, render_aabb);
+    t = advance_to_occupied(t, cone, o, d, idir, bitfield, 0, max_mip, render_aabb, coarse);
     if (t >= MAX_DEPTH) return;
     p.t = t; p.alive = 1;
 }
 
-__global__ void __launch_bounds__(SCAN_BLOCK) compact_count_kernel(uint32_t n, const NerfPayload* __restrict__ payloads, uint32_t* __restrict__ block_alive) {
-    const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x;
+__global__ void __launch_bounds__(SCAN_BLOCK) compact_count_kernel(const TraceCtl* __restrict__ prev, const NerfPayload* __restrict__ payloads, uint32_t* __restrict__ block_alive) {
+    const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x, n = prev->n_alive;
+    if (blockIdx.x * blockDim.x >= n) { if (threadIdx.x == 0) block_alive[blockIdx.x] = 0; return; }   // block-uniform: launches are sized by a host-side bound
     uint32_t total;
     block_exclusive_scan((i < n && payloads[i].alive) ? 1u : 0u, total);
     if (threadIdx.x == 0) block_alive[blockIdx.x] = total;
 }
-__global__ void __launch_bounds__(SCAN_BLOCK) compact_scatter_kernel(uint32_t n, RaysSoa src, RaysSoa dst, RaysSoa hit, const uint32_t* __restrict__ block_alive,
+__global__ void __launch_bounds__(SCAN_BLOCK) compact_scatter_kernel(const TraceCtl* __restrict__ prev, TraceCtl* __restrict__ cur, TraceCtl* __restrict__ host_copy,
+                                                                     uint32_t capacity, uint32_t target_samples, RaysSoa src, RaysSoa dst, RaysSoa hit, const uint32_t* __restrict__ block_alive,
                                                                      uint32_t* __restrict__ counters) {
-    const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x;
+    const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x, n = prev->n_alive;
+    if (i == 0) {   // loop control of the iteration that follows (counters[0] = total alive, written by the scan kernel before this launch)
+        TraceCtl c;
+        c.n_alive = counters[0];
+        c.n_steps = trace_steps(c.n_alive, capacity, target_samples);
+        c.n_elements = (c.n_alive * c.n_steps + (BATCH_GRANULARITY - 1u)) / BATCH_GRANULARITY * BATCH_GRANULARITY;   // n_alive * n_steps <= capacity < 2^32
+        c.current_step = prev->current_step + prev->n_steps;
+        *cur = c;
+        *host_copy = c;     // host-mapped: read by the host after the event recorded behind this kernel
+    }
+    if (blockIdx.x * blockDim.x >= n) return;
     const bool in = i < n;
     const bool alive = in && src.payload[i].alive;
     uint32_t total;
@@ -1297,33 +1330,60 @@ __global__ void __launch_bounds__(SCAN_BLOCK) compact_scatter_kernel(uint32_t n,
     }
 }
 
-__global__ void next_inputs_kernel(uint32_t n_alive, Aabb render_aabb, Aabb train_aabb, RaysSoa rays, float* __restrict__ input, uint32_t n_steps,
-                                   const uint8_t* __restrict__ bitfield, uint32_t max_mip, float cone_angle) {
+// generate_next_nerf_network_inputs (:948-1022): n_steps times { skip to the next occupied voxel; emit a sample; step }.
+// Written as ONE loop whose body either emits a sample or skips a voxel.  The nested form (a skip loop inside the step loop) makes a warp
+// pay the longest skip of any of its lanes once per step: lanes reach their long skips — above all the final walk out of the scene, up to
+// ~160 voxels — at different step indices, and the warp runs those walks one after the other (measured: 300 us per iteration in the tail
+// of a 3840x2160 frame, 37 us per step).  In the flat loop every lane advances on every trip whatever it is doing, and a warp takes
+// max over lanes of (samples + skips) trips.  The last bitfield byte is kept in a register: consecutive samples are 1/1024 * sqrt(3)
+// apart, a voxel is 1/128 wide and a byte covers a 2x2x2 block of voxels, so most look-ups of a ray inside a surface repeat the byte.
+// Same float operations per sample and per skip as the reference's two routines, hence the same samples.
+__global__ void next_inputs_kernel(const TraceCtl* __restrict__ ctl, Aabb render_aabb, Aabb train_aabb, RaysSoa rays, float* __restrict__ input,
+                                   const uint8_t* __restrict__ bitfield, uint32_t max_mip, float cone_angle, const uint32_t* __restrict__ coarse) {
     const Cone cone(cone_angle);
-    const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x;
+    const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x, n_alive = ctl->n_alive, n_steps = ctl->n_steps;
     if (i >= n_alive) return;
     NerfPayload& p = rays.payload[i];
     if (!p.alive) return;
     const V3 o = ld3(p.origin), d = ld3(p.dir), idir = v3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
     const V3 wd = warp_direction(d);
     float t = p.t;
-    for (uint32_t j = 0; j < n_steps; ++j) {
-        t = advance_to_occupied(t, cone, o, d, idir, bitfield, 0, max_mip, render_aabb);
-        if (t >= MAX_DEPTH) { p.n_steps = (uint16_t)j; return; }
-        const float dt = calc_dt(t, cone);
-        float* c = input + (size_t)(i + j * n_alive) * 7;
-        const V3 wp = warp_position(ray_at(o, d, t), train_aabb);
-        c[0] = wp.x; c[1] = wp.y; c[2] = wp.z; c[3] = warp_dt(dt); c[4] = wd.x; c[5] = wd.y; c[6] = wd.z;
-        t += dt;
+    uint32_t j = 0, cached_byte_idx = 0xFFFFFFFFu, cached_byte = 0;
+    while (j < n_steps) {
+        const V3 pos = ray_at(o, d, t);
+        if (t >= MAX_DEPTH || !aabb_contains(render_aabb, pos)) { p.n_steps = (uint16_t)j; return; }   // advance_to_occupied returned MAX_DEPTH (:1003-1007)
+        uint32_t mip = (uint32_t)clampi((int)mip_from_pos(pos, NERF_CASCADES - 1), 0, (int)max_mip);
+        bool occupied = true;
+        if (bitfield) {
+            occupied = !(coarse && !coarse_bit_at(coarse, pos));
+            if (occupied) {
+                const uint32_t idx = cascaded_grid_idx_at(pos, mip);
+                if (idx == 0xFFFFFFFFu) occupied = false;
+                else {
+                    const uint32_t byte_idx = idx / 8 + NERF_GRID_N_CELLS / 8 * mip;
+                    if (byte_idx != cached_byte_idx) { cached_byte_idx = byte_idx; cached_byte = __ldg(bitfield + byte_idx); }
+                    occupied = (cached_byte >> (idx % 8)) & 1u;
+                }
+            }
+        }
+        if (occupied) {
+            const float dt = calc_dt(t, cone);
+            float* c = input + (size_t)(i + j * n_alive) * 7;
+            const V3 wp = warp_position(pos, train_aabb);
+            c[0] = wp.x; c[1] = wp.y; c[2] = wp.z; c[3] = warp_dt(dt); c[4] = wd.x; c[5] = wd.y; c[6] = wd.z;
+            t += dt; ++j;
+        } else {
+            while (mip < max_mip && !density_grid_occupied_at(pos, bitfield, mip + 1)) ++mip;
+            t = advance_to_next_voxel(t, cone, pos, d, idir, mip);
+        }
     }
     p.t = t; p.n_steps = (uint16_t)n_steps;
 }
 
-__global__ void composite_kernel(uint32_t n_alive, uint32_t current_step, Aabb aabb, const float* __restrict__ camera_dev, float cam_fwd_x, float cam_fwd_y,
-                                 float cam_fwd_z, float cam_x, float cam_y, float cam_z, RaysSoa rays, const float* __restrict__ input,
-                                 const __half* __restrict__ output, uint32_t n_steps, int rgb_act, int density_act, float min_transmittance) {
-    (void)camera_dev;
-    const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x;
+__global__ void composite_kernel(const TraceCtl* __restrict__ ctl, Aabb aabb, float cam_fwd_x, float cam_fwd_y, float cam_fwd_z, float cam_x, float cam_y, float cam_z,
+                                 RaysSoa rays, const float* __restrict__ input, const __half* __restrict__ output, int rgb_act, int density_act,
+                                 float min_transmittance, int render_mode, float depth_scale) {
+    const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x, n_alive = ctl->n_alive, n_steps = ctl->n_steps, current_step = ctl->current_step;
     if (i >= n_alive) return;
     NerfPayload& p = rays.payload[i];
     if (!p.alive) return;
@@ -1340,7 +1400,14 @@ __global__ void composite_kernel(uint32_t n_alive, uint32_t current_step, Aabb a
         const float dt = unwarp_dt(in[3]);
         const float alpha = alpha_from_density(network_to_density(o[3], density_act), dt);
         const float weight = alpha * T;
-        c.x += network_to_rgb(o[0], rgb_act) * weight; c.y += network_to_rgb(o[1], rgb_act) * weight; c.z += network_to_rgb(o[2], rgb_act) * weight;
+        V3 rgb = v3(network_to_rgb(o[0], rgb_act), network_to_rgb(o[1], rgb_act), network_to_rgb(o[2], rgb_act));
+        if (render_mode != RM_SHADE) {   // :1182-1209
+            if (render_mode == RM_POSITIONS) rgb = v3((pos.x - 0.5f) / 2.0f + 0.5f, (pos.y - 0.5f) / 2.0f + 0.5f, (pos.z - 0.5f) / 2.0f + 0.5f);
+            else if (render_mode == RM_ENCODING_VIS) rgb = v3(in[0], in[1], in[2]);
+            else if (render_mode == RM_DEPTH) { const float dd = dot3(cam_fwd, pos - cam_pos) * depth_scale; rgb = v3(dd, dd, dd); }
+            else if (render_mode == RM_AO) rgb = v3(alpha, alpha, alpha);
+        }
+        c.x += rgb.x * weight; c.y += rgb.y * weight; c.z += rgb.z * weight;
         c.w += weight;
         if (weight > p.max_weight) { p.max_weight = weight; local_depth = dot3(cam_fwd, pos - cam_pos); }
         if (c.w > (1.0f - min_transmittance)) { const float a = c.w; c.x /= a; c.y /= a; c.z /= a; c.w /= a; break; }
@@ -1350,48 +1417,55 @@ __global__ void composite_kernel(uint32_t n_alive, uint32_t current_step, Aabb a
     rays.depth[i] = local_depth;
 }
 
-__global__ void shade_kernel(uint32_t n_hit, RaysSoa hit, bool linear_colors, uint32_t idx_offset, float* __restrict__ frame_rgba, float* __restrict__ frame_depth) {
+__global__ void shade_kernel(const uint32_t* __restrict__ n_hit_dev, RaysSoa hit, bool linear_colors, uint32_t W, uint32_t y0, uint32_t y_stride,
+                             float* __restrict__ frame_rgba, float* __restrict__ frame_depth, int render_mode) {
     const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x;
-    if (i >= n_hit) return;
+    if (i >= *n_hit_dev) return;
     float4 t = reinterpret_cast<const float4*>(hit.rgba)[i];
-    if (!linear_colors) { t.x = srgb_to_linear(t.x); t.y = srgb_to_linear(t.y); t.z = srgb_to_linear(t.z); }   // accumulate in linear colours
-    const uint32_t local = hit.payload[i].idx - idx_offset;
+    if (render_mode == RM_COST) { const float col = (float)hit.payload[i].n_steps / 128; t = make_float4(col, col, col, 1.0f); }
+    if (!linear_colors && (render_mode == RM_SHADE || render_mode == RM_SLICE)) { t.x = srgb_to_linear(t.x); t.y = srgb_to_linear(t.y); t.z = srgb_to_linear(t.z); }   // accumulate in linear colours
+    const uint32_t idx = hit.payload[i].idx, local = idx % W + W * ((idx / W - y0) / y_stride);
     const float4 f = reinterpret_cast<const float4*>(frame_rgba)[local];
     reinterpret_cast<float4*>(frame_rgba)[local] = make_float4(t.x + f.x * (1.0f - t.w), t.y + f.y * (1.0f - t.w), t.z + f.z * (1.0f - t.w), t.w + f.w * (1.0f - t.w));
-    if (t.w > 0.2f) frame_depth[local] = hit.depth[i];
+    if (render_mode != RM_SLICE && t.w > 0.2f) frame_depth[local] = hit.depth[i];
 }
 
 void nerf_init_rays(cudaStream_t s, const RenderCamera& cam, uint32_t sample_index, bool snap, Aabb render_aabb, const uint8_t* bitfield,
-                    uint32_t max_mip, float cone, RaysSoa rays, float* frame_rgba, float* frame_depth) {
-    NGP_PROFILE_SCOPE(s, "render_init_rays", (uint64_t)cam.res[0] * (uint64_t)(cam.y1 - cam.y0));
+                    uint32_t max_mip, float cone, RaysSoa rays, float* frame_rgba, float* frame_depth, float near_distance, const uint32_t* coarse) {
+    NGP_PROFILE_SCOPE(s, "render_init_rays", (uint64_t)cam.res[0] * (uint64_t)((cam.y1 - cam.y0 + cam.y_stride - 1) / cam.y_stride));
     const dim3 threads = {16, 8, 1};
-    const dim3 blocks = {div_round_up((uint32_t)cam.res[0], 16), div_round_up((uint32_t)(cam.y1 - cam.y0), 8), 1};
-    init_rays_kernel<<<blocks, threads, 0, s>>>(cam, sample_index, snap, render_aabb, bitfield, max_mip, cone, rays, frame_rgba, frame_depth);
+    const dim3 blocks = {div_round_up((uint32_t)cam.res[0], 16), div_round_up(div_round_up((uint32_t)(cam.y1 - cam.y0), (uint32_t)cam.y_stride), 8), 1};
+    init_rays_kernel<<<blocks, threads, 0, s>>>(cam, sample_index, snap, render_aabb, bitfield, max_mip, cone, rays, frame_rgba, frame_depth, near_distance, coarse);
     NGP_POST_LAUNCH();
 }
-void nerf_compact_rays(cudaStream_t s, uint32_t n, RaysSoa src, RaysSoa dst, RaysSoa hit, uint32_t* counters, uint32_t* scan_scratch) {
-    NGP_PROFILE_SCOPE(s, "render_compact", n);
-    const uint32_t blocks = div_round_up(n, SCAN_BLOCK);
-    compact_count_kernel<<<blocks, SCAN_BLOCK, 0, s>>>(n, src.payload, scan_scratch); NGP_POST_LAUNCH();
+void nerf_compact_rays(cudaStream_t s, uint32_t n_bound, RaysSoa src, RaysSoa dst, RaysSoa hit, uint32_t* counters, uint32_t* scan_scratch, const TraceCtl* prev,
+                       TraceCtl* cur, TraceCtl* host_copy, uint32_t capacity, uint32_t target_samples) {
+    NGP_PROFILE_SCOPE(s, "render_compact", n_bound);
+    const uint32_t blocks = std::max(div_round_up(n_bound, SCAN_BLOCK), 1u);
+    compact_count_kernel<<<blocks, SCAN_BLOCK, 0, s>>>(prev, src.payload, scan_scratch); NGP_POST_LAUNCH();
     scan_block_totals_kernel<<<1, 1024, 0, s>>>(blocks, scan_scratch, nullptr, &counters[0], nullptr, false); NGP_POST_LAUNCH();
-    compact_scatter_kernel<<<blocks, SCAN_BLOCK, 0, s>>>(n, src, dst, hit, scan_scratch, counters); NGP_POST_LAUNCH();
+    compact_scatter_kernel<<<blocks, SCAN_BLOCK, 0, s>>>(prev, cur, host_copy, capacity, target_samples, src, dst, hit, scan_scratch, counters); NGP_POST_LAUNCH();
 }
-void nerf_generate_next_inputs(cudaStream_t s, uint32_t n_alive, Aabb render_aabb, Aabb train_aabb, RaysSoa rays, float* input, uint32_t n_steps,
-                               const uint8_t* bitfield, uint32_t max_mip, float cone) {
-    NGP_PROFILE_SCOPE(s, "render_next_inputs", n_alive);
-    next_inputs_kernel<<<div_round_up(n_alive, 128), 128, 0, s>>>(n_alive, render_aabb, train_aabb, rays, input, n_steps, bitfield, max_mip, cone);
+void nerf_generate_next_inputs(cudaStream_t s, uint32_t n_bound, const TraceCtl* ctl, Aabb render_aabb, Aabb train_aabb, RaysSoa rays, float* input,
+                               const uint8_t* bitfield, uint32_t max_mip, float cone, const uint32_t* coarse) {
+    if (n_bound == 0) return;
+    NGP_PROFILE_SCOPE(s, "render_next_inputs", n_bound);
+    next_inputs_kernel<<<div_round_up(n_bound, 128), 128, 0, s>>>(ctl, render_aabb, train_aabb, rays, input, bitfield, max_mip, cone, coarse);
     NGP_POST_LAUNCH();
 }
-void nerf_composite(cudaStream_t s, uint32_t n_alive, uint32_t current_step, Aabb train_aabb, const float* camera, RaysSoa rays, const float* input,
-                    const __half* output, uint32_t n_steps, int rgb_act, int density_act, float min_transmittance) {
-    NGP_PROFILE_SCOPE(s, "render_composite", n_alive);
-    composite_kernel<<<div_round_up(n_alive, 128), 128, 0, s>>>(n_alive, current_step, train_aabb, nullptr, camera[6], camera[7], camera[8], camera[9], camera[10],
-                                                                camera[11], rays, input, output, n_steps, rgb_act, density_act, min_transmittance);
+void nerf_composite(cudaStream_t s, uint32_t n_bound, const TraceCtl* ctl, Aabb train_aabb, const float* camera, RaysSoa rays, const float* input,
+                    const __half* output, int rgb_act, int density_act, float min_transmittance, int render_mode, float depth_scale) {
+    if (n_bound == 0) return;
+    NGP_PROFILE_SCOPE(s, "render_composite", n_bound);
+    composite_kernel<<<div_round_up(n_bound, 128), 128, 0, s>>>(ctl, train_aabb, camera[6], camera[7], camera[8], camera[9], camera[10], camera[11], rays, input, output,
+                                                                rgb_act, density_act, min_transmittance, render_mode, depth_scale);
     NGP_POST_LAUNCH();
 }
-void nerf_shade(cudaStream_t s, uint32_t n_hit, RaysSoa hit, bool linear_colors, uint32_t idx_offset, float* frame_rgba, float* frame_depth) {
-    if (n_hit == 0) return;
-    shade_kernel<<<div_round_up(n_hit, 128), 128, 0, s>>>(n_hit, hit, linear_colors, idx_offset, frame_rgba, frame_depth);
+void nerf_shade(cudaStream_t s, uint32_t n_bound, const uint32_t* n_hit_dev, RaysSoa hit, bool linear_colors, const RenderCamera& cam, float* frame_rgba, float* frame_depth,
+                int render_mode) {
+    if (n_bound == 0) return;
+    shade_kernel<<<div_round_up(n_bound, 128), 128, 0, s>>>(n_hit_dev, hit, linear_colors, (uint32_t)cam.res[0], (uint32_t)cam.y0, (uint32_t)cam.y_stride, frame_rgba, frame_depth,
+                                                            render_mode);
     NGP_POST_LAUNCH();
 }
 

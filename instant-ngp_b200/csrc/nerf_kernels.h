@@ -86,24 +86,62 @@ void nerf_fill_rollover(cudaStream_t s, uint32_t n_target, const uint32_t* n_inp
 void reduce_sum_f32(cudaStream_t s, const float* in, uint32_t n, float* out_dev, float* partials /* [1024] */);
 
 // ---- inference tracer (testbed_nerf.cu:850-1230,2164-2352,2417-2693) ----
+// ERenderMode (common.h:110-121).  Normals needs the network's input gradient and is rejected by the host; Distortion and Slice have no
+// NeRF-specific compositing in the reference either and shade like Shade (Slice: no depth write).
+enum RenderMode : int { RM_AO = 0, RM_SHADE = 1, RM_NORMALS = 2, RM_POSITIONS = 3, RM_DEPTH = 4, RM_DISTORTION = 5, RM_COST = 6, RM_SLICE = 7, RM_ENCODING_VIS = 9 };
 struct NerfPayload {   // nerf.h:32-40
     float origin[3]; float dir[3]; float t; float max_weight; uint32_t idx; uint16_t n_steps; uint8_t alive; uint8_t pad;
 };
 struct RaysSoa { float* rgba; float* depth; NerfPayload* payload; };   // rgba [n][4]
 struct RenderCamera {
     int res[2]; float focal_length[2]; float screen_center[2]; float camera[12];
-    int y0, y1;     // row band rendered by this call (tile sharding); ray index = x + W*(y - y0)
+    int y0, y1;     // rows y0, y0 + y_stride, ... < y1 are rendered by this call (tile sharding: a band, or every world-th row); local ray index = x + W*((y - y0) / y_stride)
+    int y_stride;
     int lens_mode; float lens_params[4];   // m_nerf.render_lens (render_with_lens_distortion): Perspective or OpenCV
 };
+// Loop control of the wavefront tracer lives on the device (the reference reads n_alive back and synchronises every iteration,
+// testbed_nerf.cu:2540-2560): iteration `it` reads ctl[(it - 1) & 1] and its compaction writes ctl[it & 1] plus a copy into host-mapped
+// memory, which the host uses only to shrink the launch bounds and to notice the end — a few iterations late, never waiting for the GPU.
+struct TraceCtl {
+    uint32_t n_alive;        // rays still marching after this iteration's compaction
+    uint32_t n_steps;        // samples per ray this iteration: clamp(TRACE_TARGET_SAMPLES / n_alive, 1, cap) (:2574-2578), cap raised when few rays are left
+    uint32_t n_elements;     // n_alive * n_steps rounded up to the batch granularity: rows of the network call
+    uint32_t current_step;   // first step index of this iteration (the `i` of the reference's loop; Cost mode reports it)
+};
+constexpr uint32_t TRACE_MAX_STEPS = 8, TRACE_MIN_STEPS = 1;   // :97-100
+// samples per iteration the schedule aims for.  The reference uses 2 Mi (:2574), sized for the memory of a desktop GPU; a 3840 x 2160 frame then
+// spends its first 20 iterations at one sample per ray, paying the compaction, seven launches and every per-ray load once per sample.  8 Mi
+// (0.5 GB of sample rows: nothing on a 180 GB part) starts such a frame at 5 samples per ray: 40 -> 19 iterations, 17.9 -> 15.0 ms
+// (16 Mi: 15.2 ms — the samples wasted behind a ray's last one grow with the step count).  NGP_TRACE_TARGET_SAMPLES overrides (experiments).
+constexpr uint32_t TRACE_TARGET_SAMPLES = 8u * 1024u * 1024u;
+constexpr uint32_t TRACE_MAX_STEPS_TAIL = 32;     // see trace_steps()
+// samples per ray and iteration.  The reference's schedule up to 8; beyond that only when so few rays are alive that an iteration is bound
+// by launch latency, not throughput (<= 131072: 16, <= 32768: 32) — a ray's result does not depend on the schedule (the compositor consumes
+// samples in order and stops at the same one), only the number of iterations does; `capacity` = rows the sample buffers hold
+NGP_HD uint32_t trace_steps(uint32_t n_alive, uint32_t capacity, uint32_t target_samples) {
+    if (n_alive == 0) return 0;
+    const uint32_t cap = n_alive <= 32768u ? TRACE_MAX_STEPS_TAIL : (n_alive <= 131072u ? 16u : TRACE_MAX_STEPS);
+    uint32_t k = target_samples / n_alive;
+    k = k < TRACE_MIN_STEPS ? TRACE_MIN_STEPS : (k > cap ? cap : k);
+    const uint32_t fit = capacity / n_alive;
+    return k > fit ? (fit > 0 ? fit : 1u) : k;
+}
+// coarse (optional): 32^3 dilated occupancy bits of the unit cube (nerf_build_coarse_occupancy); rays that cannot touch an occupied cell
+// are not walked and look-ups inside empty coarse cells are not made — same results, see the kernels
 void nerf_init_rays(cudaStream_t s, const RenderCamera& cam, uint32_t sample_index, bool snap_to_pixel_centers, Aabb render_aabb,
-                    const uint8_t* bitfield, uint32_t max_mip, float cone_angle, RaysSoa rays, float* frame_rgba, float* frame_depth);
-// alive -> dst (compacted, order preserving), finished with alpha > 0.001 -> hit ; counters[0] = n_alive, counters[1] += n_hit
-void nerf_compact_rays(cudaStream_t s, uint32_t n, RaysSoa src, RaysSoa dst, RaysSoa hit, uint32_t* counters, uint32_t* scan_scratch);
-void nerf_generate_next_inputs(cudaStream_t s, uint32_t n_alive, Aabb render_aabb, Aabb train_aabb, RaysSoa rays, float* network_input /*[n_alive*k][7]*/,
-                               uint32_t n_steps, const uint8_t* bitfield, uint32_t max_mip, float cone_angle);
-void nerf_composite(cudaStream_t s, uint32_t n_alive, uint32_t current_step, Aabb train_aabb, const float* camera, RaysSoa rays,
-                    const float* network_input, const __half* network_output, uint32_t n_steps, int rgb_activation, int density_activation,
-                    float min_transmittance);
-void nerf_shade(cudaStream_t s, uint32_t n_hit, RaysSoa hit, bool linear_colors, uint32_t idx_offset, float* frame_rgba, float* frame_depth);
+                    const uint8_t* bitfield, uint32_t max_mip, float cone_angle, RaysSoa rays, float* frame_rgba, float* frame_depth, float near_distance = 0.f,
+                    const uint32_t* coarse = nullptr);
+// alive -> dst (compacted, order preserving), finished with alpha > 0.001 -> hit ; counters[0] = n_alive, counters[1] += n_hit.
+// n_bound >= prev->n_alive sizes the launch; writes *cur (and *host_copy, host-mapped) for the iteration that follows
+void nerf_compact_rays(cudaStream_t s, uint32_t n_bound, RaysSoa src, RaysSoa dst, RaysSoa hit, uint32_t* counters, uint32_t* scan_scratch,
+                       const TraceCtl* prev, TraceCtl* cur, TraceCtl* host_copy, uint32_t capacity, uint32_t target_samples);
+void nerf_generate_next_inputs(cudaStream_t s, uint32_t n_bound, const TraceCtl* ctl, Aabb render_aabb, Aabb train_aabb, RaysSoa rays,
+                               float* network_input /*[n_alive*k][7]*/, const uint8_t* bitfield, uint32_t max_mip, float cone_angle, const uint32_t* coarse = nullptr);
+void nerf_composite(cudaStream_t s, uint32_t n_bound, const TraceCtl* ctl, Aabb train_aabb, const float* camera, RaysSoa rays,
+                    const float* network_input, const __half* network_output, int rgb_activation, int density_activation,
+                    float min_transmittance, int render_mode = RM_SHADE, float depth_scale = 1.f);
+// n_hit_dev: number of finished rays (counters[1]); n_bound sizes the launch
+void nerf_shade(cudaStream_t s, uint32_t n_bound, const uint32_t* n_hit_dev, RaysSoa hit, bool linear_colors, const RenderCamera& cam, float* frame_rgba, float* frame_depth,
+                int render_mode = RM_SHADE);
 
 }  // namespace ngp

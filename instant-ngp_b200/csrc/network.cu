@@ -91,10 +91,10 @@ void NerfNetwork::initialize_params(uint64_t seed, float* master_dev, cudaStream
     grid_init(s, grid, rng, master_dev + off_grid);
 }
 
-void NerfNetwork::inference(cudaStream_t s, const __half* params, const float* coords, uint32_t n, __half* out) {
+void NerfNetwork::inference(cudaStream_t s, const __half* params, const float* coords, uint32_t n, __half* out, const uint32_t* n_dyn) {
     __half* enc = enc_buf.get<__half>((size_t)n * dims.pos_width);
-    grid_forward(s, grid, params + off_grid, coords, 7, n, enc, LAYOUT_BLK8);
-    nerf_mlp_forward(s, dims, params + off_density, params + off_rgb, enc, coords, n, out);
+    grid_forward(s, grid, params + off_grid, coords, 7, n, enc, LAYOUT_BLK8, n_dyn);
+    nerf_mlp_forward(s, dims, params + off_density, params + off_rgb, enc, coords, n, out, n_dyn);
 }
 
 void NerfNetwork::density(cudaStream_t s, const __half* params, const float* pos, uint32_t pos_stride, uint32_t n, __half* out) {

@@ -41,7 +41,7 @@ struct NerfNetwork {
     explicit NerfNetwork(const Json& config);
     void initialize_params(uint64_t seed, float* master_dev, cudaStream_t s);
     // coords [n][7] fp32; out [n][4] fp16 ; n % 128 == 0
-    void inference(cudaStream_t s, const __half* params, const float* coords, uint32_t n, __half* out);
+    void inference(cudaStream_t s, const __half* params, const float* coords, uint32_t n, __half* out, const uint32_t* n_dyn = nullptr);
     // pos [n][pos_stride] fp32; out [n] fp16 (raw density)
     void density(cudaStream_t s, const __half* params, const float* pos, uint32_t pos_stride, uint32_t n, __half* out);
     // forward(recompute)+backward; grads: param-shaped fp16, OVERWRITTEN (EGradientMode::Overwrite, testbed_nerf.cu:4078)

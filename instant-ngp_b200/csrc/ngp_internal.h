@@ -32,8 +32,10 @@ struct GridLayout {
 void grid_make_layout(GridLayout& g, uint32_t n_dims, uint32_t n_levels, uint32_t n_features, uint32_t log2_hashmap_size,
                       uint32_t base_resolution, float per_level_scale);
 // y: [n_rows_padded x C] fp16 in `y_layout`; rows [0,n) are written (n_levels*F.. C zero-filled)
+// n_dyn (optional, device memory): the kernels process min(n, *n_dyn) rows; n sizes the launch.  Used by the inference tracer, whose row
+// count per iteration is produced on the device by the ray-compaction kernel
 void grid_forward(cudaStream_t s, const GridLayout& g, const __half* table, const float* x, uint32_t x_stride, uint32_t n,
-                  __half* y, int y_layout);
+                  __half* y, int y_layout, const uint32_t* n_dyn = nullptr);
 // grad += scatter(w * dy); grad is table-shaped fp16 (caller zeroes it for EGradientMode::Overwrite)
 void grid_backward(cudaStream_t s, const GridLayout& g, const float* x, uint32_t x_stride, uint32_t n, const __half* dy,
                    int dy_layout, __half* grad);
@@ -65,7 +67,7 @@ inline uint32_t mlp_n_params(uint32_t in_w, uint32_t n_hidden) { return MLP_WIDT
 // Inference of the whole NeRF network on n (multiple of 128) samples.
 //   enc: [n x pos_width] blk8 fp16 ; coords: [n][7] fp32 (dir at +4) ; out: [n][4] fp16 (r,g,b,sigma raw)
 void nerf_mlp_forward(cudaStream_t s, const NerfNetDims& d, const __half* w_density, const __half* w_rgb, const __half* enc,
-                      const float* coords, uint32_t n, __half* out);
+                      const float* coords, uint32_t n, __half* out, const uint32_t* n_dyn = nullptr);
 // density net only: out [n] fp16 (channel 0)
 void nerf_mlp_density(cudaStream_t s, const NerfNetDims& d, const __half* w_density, const __half* enc, uint32_t n, __half* out);
 // Forward recompute + backward on n samples.  dL_dout: [n][4] fp16.  Outputs: dL_denc [n x pos_width] blk8 fp16,

@@ -160,7 +160,7 @@ void Testbed::save_snapshot(cudaStream_t s, const std::string& path, bool includ
     snap["loss"] = Json::number(m_loss_scalar);
     snap["aabb"] = aabb_json(aabb);
     snap["render_aabb"] = aabb_json(render_aabb);
-    snap["background_color"] = vec_json(background_color, 3);
+    snap["background_color"] = vec_json(background_color, 4);
     Json cfg = m_config; cfg["snapshot"] = snap;
 
     std::string bytes;
@@ -264,7 +264,7 @@ void Testbed::load_snapshot(cudaStream_t s, const std::string& path) {
     }
     if (snap.contains("aabb")) aabb_from_json(snap.at("aabb"), aabb);
     if (snap.contains("render_aabb")) aabb_from_json(snap.at("render_aabb"), render_aabb);
-    if (snap.contains("background_color")) for (int k = 0; k < 3; ++k) background_color[k] = (float)snap.at("background_color").arr.at(k).num;
+    if (snap.contains("background_color")) for (size_t k = 0; k < std::min<size_t>(4, snap.at("background_color").arr.size()); ++k) background_color[k] = (float)snap.at("background_color").arr.at(k).num;
 
     // m_network_config = config; reset_network(false); then counters, Trainer::deserialize (testbed.cu:5028-5040)
     const uint32_t rays_per_batch = m_rays_per_batch, measured = m_measured, measured_before = m_measured_before;

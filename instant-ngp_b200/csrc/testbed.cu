@@ -33,6 +33,7 @@ static bool has_mask_pixels(const void* pixels, size_t n_pixels) {
 
 Testbed::Testbed(int mode) : m_mode(mode), m_rng(1337), m_density_grid_rng(1337) {
     NGP_CHECK(mode == MODE_TB_NERF || mode == MODE_TB_IMAGE || mode == MODE_TB_SDF, "Testbed: unknown mode (Nerf = 0, Sdf = 1, Image = 2)");
+    reset_camera();
 }
 
 Testbed::~Testbed() {
@@ -41,6 +42,7 @@ Testbed::~Testbed() {
     if (m_ev_prefetch) cudaEventDestroy(m_ev_prefetch);
     if (m_ev_after_mlp) cudaEventDestroy(m_ev_after_mlp);
     if (m_ev_after_loss) cudaEventDestroy(m_ev_after_loss);
+    if (m_trace_host) { cudaFreeHost(m_trace_host); for (cudaEvent_t e : m_ev_trace) if (e) cudaEventDestroy(e); }
     if (m_comm_stream) { cudaStreamSynchronize(m_comm_stream); cudaStreamDestroy(m_comm_stream); }
     if (m_copy_stream) { cudaStreamSynchronize(m_copy_stream); cudaStreamDestroy(m_copy_stream); }
     for (cudaEvent_t e : {m_ev_copy_gate, m_ev_copy_done}) if (e) cudaEventDestroy(e);
@@ -594,8 +596,10 @@ void Testbed::train_image_step(cudaStream_t s, uint32_t n, bool get_loss) {
     float* pos = m_img_pos.get<float>((size_t)n * 2); float* target = m_img_target.get<float>((size_t)n * 3);
     __half* out = m_img_out.get<__half>((size_t)n * 16); __half* dl = m_img_dl.get<__half>((size_t)n * 16);
     float* lossv = m_img_loss.get<float>(n); m_loss_sum.get<float>(4); m_partials.get<float>(1024);
-    image_generate_batch(s, n, m_rng, image_stratified, m_image.as<float>(), m_image_w, m_image_h, image_snap_to_pixel_centers, image_linear_colors, pos, target);
-    m_rng.advance();
+    NGP_CHECK(image_random_mode >= IMG_RANDOM_RANDOM && image_random_mode <= IMG_RANDOM_STRATIFIED, "image.random_mode: unknown mode");
+    image_generate_batch(s, n, m_rng, image_random_mode, (size_t)n * m_training_step, (uint32_t)seed, m_image.as<float>(), m_image_w, m_image_h,
+                         image_snap_to_pixel_centers, image_linear_colors, pos, target);
+    if (image_random_mode == IMG_RANDOM_RANDOM || image_random_mode == IMG_RANDOM_STRATIFIED) m_rng.advance();   // the low-discrepancy modes do not draw from m_rng
     m_image_net->inference(s, m_trainer->params, pos, 2, n, out);
     tcnn_loss(s, m_tcnn_loss, n, 3, out, target, LOSS_SCALE, dl, get_loss ? lossv : nullptr);
     if (get_loss) reduce_sum_f32(s, lossv, n, m_loss_sum.as<float>(), m_partials.as<float>());
@@ -664,55 +668,165 @@ float Testbed::compute_image_mse(cudaStream_t s, bool quantize) {
 // ---------------------------------------------------------------------------------------------------------------
 // render_nerf + NerfTracer::trace (testbed_nerf.cu:2417-2693,2752-2871), Shade mode, headless float4 buffer
 // ---------------------------------------------------------------------------------------------------------------
-__global__ void accumulate_kernel(uint32_t n, const float* __restrict__ frame, float* __restrict__ accum, float w_new) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) accum[i] = accum[i] * (1.0f - w_new) + frame[i] * w_new;
-}
-
-void Testbed::render(cudaStream_t s, const float* camera_matrix, const float* focal_length, const float* screen_center, int w, int h, int spp, int y0, int y1,
-                     float* rgba_out, bool out_is_device, float* depth_out) {
-    NGP_CHECK(m_mode == MODE_TB_NERF && m_nerf_net && m_trainer, "render: NeRF network not initialised");
-    NGP_CHECK(w > 0 && h > 0 && y0 >= 0 && y1 <= h && y0 < y1 && spp >= 1, "render: bad resolution / row band");
-    NGP_CHECK(!m_inference_stale, "render: sharded optimizer — call sync_inference_params (collective, every rank) first");
-    const uint32_t n_pixels = (uint32_t)w * (uint32_t)(y1 - y0);
+void Testbed::trace_sample(cudaStream_t s, const RenderCamera& cam, int sample, float* frame, float* fdepth) {
+    NGP_CHECK(render_mode != RM_NORMALS, "render_mode Normals needs the network's input gradient: not implemented in this library");
+    const uint32_t n_pixels = (uint32_t)cam.res[0] * (uint32_t)((cam.y1 - cam.y0 + cam.y_stride - 1) / cam.y_stride);
     const uint32_t n_pad = (uint32_t)next_multiple(n_pixels, BATCH_GRANULARITY);
     RaysSoa rays[3];
     for (int k = 0; k < 3; ++k) rays[k] = {m_r_rgba[k].get<float>((size_t)n_pad * 4), m_r_depth[k].get<float>(n_pad), m_r_payload[k].get<NerfPayload>(n_pad)};
-    constexpr uint32_t MAX_STEPS = 8, MIN_STEPS = 1, MARCH_ITER = 10000;   // :97-100
-    float* input = m_r_input.get<float>((size_t)n_pad * MAX_STEPS * 7); __half* output = m_r_output.get<__half>((size_t)n_pad * MAX_STEPS * 4);
-    uint32_t* counters = m_r_counters.get<uint32_t>(4); uint32_t* scan = m_r_scan.get<uint32_t>(div_round_up(n_pad, 256) + 1);
+    // rows the sample buffers hold.  An iteration asks for n_alive * clamp(target / n_alive, 1, cap) <= max(n_alive, target) rows, so max(n_pixels, target)
+    // covers every case (the reference allocates n_pixels * MAX_STEPS rows, 2.4 GB at 3840 x 2160); small frames need no more than 32 steps per ray
+    static const uint32_t target = [] { const char* e = getenv("NGP_TRACE_TARGET_SAMPLES"); return e ? (uint32_t)atol(e) : TRACE_TARGET_SAMPLES; }();
+    const uint32_t capacity = (uint32_t)std::max<uint64_t>(n_pad, std::min<uint64_t>(target, (uint64_t)n_pad * TRACE_MAX_STEPS_TAIL));
+    float* input = m_r_input.get<float>((size_t)capacity * 7); __half* output = m_r_output.get<__half>((size_t)capacity * 4);
+    uint32_t* counters = m_r_counters.get<uint32_t>(4 + 2 * sizeof(TraceCtl) / 4); uint32_t* scan = m_r_scan.get<uint32_t>(div_round_up(n_pad, 256) + 1);
+    TraceCtl* ctl = reinterpret_cast<TraceCtl*>(counters + 4);
+    constexpr uint32_t RING = 8, LAG = 2;     // the host trails the device by LAG iterations when it reads the loop control back
+    if (!m_trace_host) {
+        NGP_CUDA_CHECK(cudaHostAlloc(reinterpret_cast<void**>(&m_trace_host), (RING + 1) * sizeof(TraceCtl), cudaHostAllocMapped));
+        for (cudaEvent_t& e : m_ev_trace) NGP_CUDA_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    }
+    const float depth_scale = 1.0f / m_ds_scale;   // render_nerf: 1 / dataset.scale
+    // the coarse table speeds up walks that stay inside the unit cube at mip 0; rebuilt per call (4 KB) so that it always matches the bitfield
+    const bool unit_cube = m_max_cascade == 0 && render_aabb.min[0] >= 0.f && render_aabb.min[1] >= 0.f && render_aabb.min[2] >= 0.f &&
+                           render_aabb.max[0] <= 1.f && render_aabb.max[1] <= 1.f && render_aabb.max[2] <= 1.f;
+    static const bool no_coarse = getenv("NGP_TRACE_NO_COARSE") != nullptr;
+    const uint32_t* coarse = nullptr;
+    if (unit_cube && !no_coarse) { uint32_t* c = m_r_coarse.get<uint32_t>(1024); nerf_build_coarse_occupancy(s, m_bitfield.as<uint8_t>(), c); coarse = c; }
+    nerf_init_rays(s, cam, (uint32_t)sample, snap_to_pixel_centers, render_aabb, m_bitfield.as<uint8_t>(), m_max_cascade, cone_angle_constant, rays[0], frame, fdepth,
+                   render_near_distance, coarse);
+    // ctl[0] = state before the first compaction: every pixel is a ray, step index 1 (the reference's loop starts at i = 1)
+    TraceCtl* boot = m_trace_host + RING;
+    *boot = TraceCtl{n_pixels, 0, 0, 1};
+    NGP_CUDA_CHECK(cudaMemsetAsync(counters, 0, 16, s));
+    NGP_CUDA_CHECK(cudaMemcpyAsync(&ctl[0], boot, sizeof(TraceCtl), cudaMemcpyHostToDevice, s));
+    uint32_t bound = n_pixels, db = 0;
+    for (uint32_t it = 1;; ++it) {
+        RaysSoa& cur = rays[(db + 1) % 2]; RaysSoa& tmp = rays[db % 2]; ++db;
+        const TraceCtl* prev = &ctl[(it - 1) & 1]; TraceCtl* now = &ctl[it & 1];
+        nerf_compact_rays(s, bound, tmp, cur, rays[2], counters, scan, prev, now, m_trace_host + it % RING, capacity, target);
+        NGP_CUDA_CHECK(cudaEventRecord(m_ev_trace[it % RING], s));
+        // rows of this iteration's network call are bounded by what `bound` rays can ask for; the kernels read the true counts from `now`
+        const uint32_t rows_bound = (uint32_t)std::min<uint64_t>(capacity, next_multiple(std::max<uint64_t>(bound, std::min<uint64_t>(target, (uint64_t)bound * TRACE_MAX_STEPS_TAIL)), (uint64_t)BATCH_GRANULARITY));
+        nerf_generate_next_inputs(s, bound, now, render_aabb, aabb, cur, input, m_bitfield.as<uint8_t>(), m_max_cascade, cone_angle_constant, coarse);
+        m_nerf_net->inference(s, m_trainer->inference_params, input, rows_bound, output, &now->n_elements);
+        nerf_composite(s, bound, now, aabb, cam.camera, cur, input, output, rgb_activation, density_activation, render_min_transmittance, render_mode, depth_scale);
+        if (it >= LAG) {   // what iteration it - LAG + 1 left alive (long since computed unless the frame is tiny): tighter bounds, and the end
+            const uint32_t seen = it - LAG + 1;
+            NGP_CUDA_CHECK(cudaEventSynchronize(m_ev_trace[seen % RING]));
+            const uint32_t alive = m_trace_host[seen % RING].n_alive;
+            if (alive == 0) break;      // iterations seen + 1 .. it were enqueued with nothing to do and fall through
+            bound = std::min(bound, alive);
+        }
+        NGP_CHECK(it < 10000, "render: ray marching did not terminate");   // MARCH_ITER (:100)
+    }
+    nerf_shade(s, n_pixels, counters + 1, rays[2], linear_colors, cam, frame, fdepth, render_mode);
+}
+
+void Testbed::render(cudaStream_t s, const float* camera_matrix, const float* focal_length, const float* screen_center_, int w, int h, int spp, int y0, int y1,
+                     float* rgba_out, bool out_is_device, float* depth_out) {
+    NGP_CHECK(m_mode == MODE_TB_NERF && m_nerf_net && m_trainer, "render: NeRF network not initialised");
+    NGP_CHECK(w > 0 && h > 0 && y0 >= 0 && y1 <= h && y0 < y1 && spp >= 1 && render_row_stride >= 1, "render: bad resolution / row band");
+    NGP_CHECK(!m_inference_stale, "render: sharded optimizer — call sync_inference_params (collective, every rank) first");
+    const uint32_t n_pixels = (uint32_t)w * (uint32_t)((y1 - y0 + render_row_stride - 1) / render_row_stride);
     float* frame = m_frame.get<float>((size_t)n_pixels * 4); float* fdepth = m_frame_depth.get<float>(n_pixels); float* accum = m_accum.get<float>((size_t)n_pixels * 4);
     RenderCamera cam{};
-    cam.res[0] = w; cam.res[1] = h; cam.y0 = y0; cam.y1 = y1;
-    memcpy(cam.focal_length, focal_length, 8); memcpy(cam.screen_center, screen_center, 8); memcpy(cam.camera, camera_matrix, 48);
+    cam.res[0] = w; cam.res[1] = h; cam.y0 = y0; cam.y1 = y1; cam.y_stride = render_row_stride;
+    memcpy(cam.focal_length, focal_length, 8); memcpy(cam.screen_center, screen_center_, 8); memcpy(cam.camera, camera_matrix, 48);
     cam.lens_mode = render_lens_mode; memcpy(cam.lens_params, render_lens_params, 16);
     NGP_CUDA_CHECK(cudaMemsetAsync(accum, 0, (size_t)n_pixels * 16, s));
     for (int sample = 0; sample < spp; ++sample) {
-        nerf_init_rays(s, cam, (uint32_t)sample, snap_to_pixel_centers, render_aabb, m_bitfield.as<uint8_t>(), m_max_cascade, cone_angle_constant, rays[0], frame, fdepth);
-        NGP_CUDA_CHECK(cudaMemsetAsync(counters, 0, 16, s));
-        uint32_t n_alive = n_pixels, i = 1, db = 0;
-        while (i < MARCH_ITER) {
-            RaysSoa& cur = rays[(db + 1) % 2]; RaysSoa& tmp = rays[db % 2]; ++db;
-            nerf_compact_rays(s, n_alive, tmp, cur, rays[2], counters, scan);
-            NGP_CUDA_CHECK(cudaMemcpyAsync(&n_alive, counters, 4, cudaMemcpyDeviceToHost, s));
-            NGP_CUDA_CHECK(cudaStreamSynchronize(s));
-            if (n_alive == 0) break;
-            const uint32_t k = std::min(std::max(2u * 1024u * 1024u / n_alive, MIN_STEPS), MAX_STEPS);   // :2574-2578
-            nerf_generate_next_inputs(s, n_alive, render_aabb, aabb, cur, input, k, m_bitfield.as<uint8_t>(), m_max_cascade, cone_angle_constant);
-            const uint32_t n_elements = (uint32_t)next_multiple((uint64_t)n_alive * k, BATCH_GRANULARITY);
-            m_nerf_net->inference(s, m_trainer->inference_params, input, n_elements, output);
-            nerf_composite(s, n_alive, i, aabb, cam.camera, cur, input, output, k, rgb_activation, density_activation, render_min_transmittance);
-            i += k;
-        }
-        uint32_t n_hit = 0;
-        NGP_CUDA_CHECK(cudaMemcpyAsync(&n_hit, counters + 1, 4, cudaMemcpyDeviceToHost, s));
-        NGP_CUDA_CHECK(cudaStreamSynchronize(s));
-        nerf_shade(s, n_hit, rays[2], linear_colors, (uint32_t)y0 * (uint32_t)w, frame, fdepth);
-        accumulate_kernel<<<div_round_up(n_pixels * 4, 256), 256, 0, s>>>(n_pixels * 4, frame, accum, 1.0f / (float)(sample + 1));
-        NGP_POST_LAUNCH();
+        trace_sample(s, cam, sample, frame, fdepth);
+        frame_accumulate(s, n_pixels, frame, accum, (float)sample, CS_LINEAR);
     }
     NGP_CUDA_CHECK(cudaMemcpyAsync(rgba_out, accum, (size_t)n_pixels * 16, out_is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, s));
     if (depth_out) NGP_CUDA_CHECK(cudaMemcpyAsync(depth_out, fdepth, (size_t)n_pixels * 4, out_is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, s));
+    NGP_CUDA_CHECK(cudaStreamSynchronize(s));
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// view state (testbed.cu:789-880,3810-3824) and render_to_cpu / render_frame with the output stage (python_api.cu:127-205,
+// testbed.cu:4640-4760)
+// ---------------------------------------------------------------------------------------------------------------
+void Testbed::set_fov(float degrees) {   // fov_to_focal_length(1, degrees)
+    relative_focal_length[0] = relative_focal_length[1] = 0.5f / tanf(0.5f * degrees * 3.14159265358979323846f / 180.0f);
+}
+float Testbed::fov() const {             // focal_length_to_fov(1, relative_focal_length[fov_axis])
+    return 2.0f * 180.0f / 3.14159265358979323846f * atanf(1.0f / (relative_focal_length[fov_axis] * 2.0f));
+}
+void Testbed::reset_camera() {
+    fov_axis = 1; zoom = 1.0f; screen_center[0] = screen_center[1] = 0.5f;
+    if (m_mode == MODE_TB_IMAGE) { relative_focal_length[0] = relative_focal_length[1] = 1.0f; scale = 1.0f; }
+    else { set_fov(50.625f); scale = 1.5f; }
+    const float m[12] = {1, 0, 0, 0, -1, 0, 0, 0, -1, 0.5f, 0.5f, 0.5f};
+    memcpy(camera, m, sizeof(m));
+    for (int k = 0; k < 3; ++k) camera[9 + k] -= scale * camera[6 + k];
+}
+void Testbed::set_nerf_camera_matrix(const float* nerf) {   // NerfDataset::nerf_matrix_to_ngp (nerf_loader.h:120-140)
+    float m[12]; memcpy(m, nerf, sizeof(m));
+    for (int r = 0; r < 3; ++r) { m[3 + r] *= -1.f; m[6 + r] *= -1.f; m[9 + r] = m[9 + r] * m_ds_scale + m_ds_offset[r]; }
+    for (int c = 0; c < 4; ++c) { camera[c * 3 + 0] = m[c * 3 + 1]; camera[c * 3 + 1] = m[c * 3 + 2]; camera[c * 3 + 2] = m[c * 3 + 0]; }
+}
+void Testbed::set_camera_to_training_view(int v) {
+    NGP_CHECK(m_mode == MODE_TB_NERF && v >= 0 && v < (int)m_n_images, "set_camera_to_training_view: no such training view");
+    const ImageMeta& m = m_host_metas[v];
+    float old_look_at[3]; for (int k = 0; k < 3; ++k) old_look_at[k] = camera[9 + k] + camera[6 + k] * scale;
+    memcpy(camera, m.xform, sizeof(camera));
+    for (int k = 0; k < 2; ++k) relative_focal_length[k] = m.focal_length[k] / (float)m.res[fov_axis];
+    float d = 0.f; for (int k = 0; k < 3; ++k) d += (old_look_at[k] - camera[9 + k]) * camera[6 + k];
+    scale = std::max(d, 0.1f);
+    render_with_lens_distortion = true;
+    render_lens_mode = m.lens_mode; memcpy(render_lens_params, m.lens_params, sizeof(render_lens_params));
+    for (int k = 0; k < 2; ++k) screen_center[k] = 1.0f - m.principal_point[k];
+    training_view = v;
+}
+void Testbed::apply_dataset_view_hints(bool has_render_aabb, const float* ra, const float* up3) {
+    if (has_render_aabb) {   // m_render_aabb = dataset.render_aabb.intersection(m_aabb)
+        for (int k = 0; k < 3; ++k) { render_aabb.min[k] = std::max(ra[k], aabb.min[k]); render_aabb.max[k] = std::min(ra[3 + k], aabb.max[k]); }
+    }
+    for (int k = 0; k < 3; ++k) up_dir[k] = up3[k];
+}
+
+void Testbed::render_frame(cudaStream_t s, int w, int h, int spp, bool to_srgb, int y0, int y1, float* rgba_out, bool out_is_device) {
+    NGP_CHECK(m_mode == MODE_TB_NERF, "render: implemented for the Nerf mode");
+    NGP_CHECK(w > 0 && h > 0 && y0 >= 0 && y1 <= h && y0 < y1 && spp >= 1 && render_row_stride >= 1, "render: bad resolution / row band");
+    NGP_CHECK(!(render_ground_truth && render_row_stride != 1), "render_ground_truth: row_stride must be 1");
+    NGP_CHECK(color_space >= CS_LINEAR && color_space <= CS_VISPOSNEG && tonemap_curve >= TM_IDENTITY && tonemap_curve <= TM_REINHARD, "render: bad color_space / tonemap_curve");
+    const bool gt_only = render_ground_truth && ground_truth_alpha >= 1.0f;
+    if (!gt_only) {
+        NGP_CHECK(m_nerf_net && m_trainer, "render: NeRF network not initialised");
+        NGP_CHECK(!m_inference_stale, "render: sharded optimizer — call sync_inference_params (collective, every rank) first");
+    }
+    const uint32_t n_pixels = (uint32_t)w * (uint32_t)((y1 - y0 + render_row_stride - 1) / render_row_stride);
+    float* frame = m_frame.get<float>((size_t)n_pixels * 4); float* fdepth = m_frame_depth.get<float>(n_pixels); float* accum = m_accum.get<float>((size_t)n_pixels * 4);
+    float* surface = m_surface.get<float>((size_t)n_pixels * 4);
+    RenderCamera cam{};
+    cam.res[0] = w; cam.res[1] = h; cam.y0 = y0; cam.y1 = y1; cam.y_stride = render_row_stride;
+    const int res[2] = {w, h};
+    for (int k = 0; k < 2; ++k) {
+        cam.focal_length[k] = relative_focal_length[k] * (float)res[fov_axis] * zoom;     // calc_focal_length
+        cam.screen_center[k] = (0.5f - screen_center[k]) * zoom + 0.5f;                    // render_screen_center
+    }
+    memcpy(cam.camera, camera, sizeof(camera));
+    if (render_with_lens_distortion) { cam.lens_mode = render_lens_mode; memcpy(cam.lens_params, render_lens_params, 16); }
+    const int out_cs = to_srgb ? CS_SRGB : CS_LINEAR;
+    NGP_CUDA_CHECK(cudaMemsetAsync(accum, 0, (size_t)n_pixels * 16, s));
+    for (int sample = 0; sample < spp; ++sample) {
+        if (gt_only) NGP_CUDA_CHECK(cudaMemsetAsync(frame, 0, (size_t)n_pixels * 16, s));   // the frame buffer is cleared, nothing is traced
+        else trace_sample(s, cam, sample, frame, fdepth);
+        frame_accumulate(s, n_pixels, frame, accum, (float)sample, color_space);
+    }
+    frame_tonemap(s, n_pixels, exposure, background_color, accum, color_space, out_cs, tonemap_curve, false, false, surface);
+    if (render_ground_truth) {
+        NGP_CHECK(training_view >= 0 && training_view < (int)m_n_images, "render_ground_truth: no training view selected");
+        const ImageMeta& m = m_host_metas[training_view];
+        NGP_CHECK(m.pixels, "render_ground_truth: the training view has no pixels (metadata restored from a snapshot)");
+        const float e3[3] = {exposure, exposure, exposure};   // + cam_exposure[view], which this library does not optimise (zero)
+        const float centre[2] = {0.5f, 0.5f};
+        frame_overlay_image(s, w, h, y0, y1, ground_truth_alpha, e3, background_color, out_cs, m.pixels, m.data_type, m.res, tonemap_curve, color_space, fov_axis, zoom,
+                            centre, surface);
+    }
+    NGP_CUDA_CHECK(cudaMemcpyAsync(rgba_out, surface, (size_t)n_pixels * 16, out_is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, s));
     NGP_CUDA_CHECK(cudaStreamSynchronize(s));
 }
 

@@ -6,6 +6,7 @@
 #include "nerf_kernels.h"
 #include "image_kernels.h"
 #include "sdf_kernels.h"
+#include "frame_output.h"
 #include "comm.h"
 #include <memory>
 #include <vector>
@@ -69,6 +70,18 @@ public:
     // render_nerf (testbed_nerf.cu:2752-2871) into a host or device float4 buffer, rows [y0,y1), averaged over spp
     void render(cudaStream_t s, const float* camera_matrix, const float* focal_length, const float* screen_center, int w, int h, int spp, int y0, int y1,
                 float* rgba_out, bool out_is_device, float* depth_out);
+    // Testbed::render_to_cpu -> render_frame (python_api.cu:127-205, testbed.cu:4480-4760), headless: rows [y0,y1) of a w x h frame seen by the
+    // testbed's OWN camera (camera / relative_focal_length / fov_axis / zoom / screen_center below), spp samples accumulated in
+    // `color_space`, then background + exposure + tonemap curve + output colour space (sRGB when to_srgb), then the ground-truth overlay
+    // when render_ground_truth is set (with ground_truth_alpha >= 1 the network is not traced at all, as in the reference)
+    void render_frame(cudaStream_t s, int w, int h, int spp, bool to_srgb, int y0, int y1, float* rgba_out, bool out_is_device);
+    // view state helpers (testbed.cu:789-880,3810-3824)
+    void reset_camera();
+    void set_fov(float degrees);
+    float fov() const;
+    void set_nerf_camera_matrix(const float* nerf_mat4x3_col_major);
+    void set_camera_to_training_view(int trainview);
+    void apply_dataset_view_hints(bool has_render_aabb, const float* render_aabb6, const float* up3);   // load_nerf_post :3096-3111
     float compute_image_mse(cudaStream_t s, bool quantize);   // testbed_image.cu:465-527
     // save_snapshot / load_snapshot (testbed.cu:4873-5057): the network config plus a "snapshot" object (fp16 inference parameters,
     // fp16 density grid, counters, optionally the optimizer state) as MessagePack; ".ingp" = the same inside a zlib stream
@@ -91,9 +104,20 @@ public:
     // Testbed::m_snap_to_pixel_centers (render rays, default false, python_api.cu:478)
     bool train_snap_to_pixel_centers = true, snap_to_pixel_centers = false;
     float near_distance = 0.1f, density_grid_decay = 0.95f, render_min_transmittance = 0.01f, cone_angle_constant = 0.0f;
-    float background_color[3] = {0.f, 0.f, 0.f};
+    float background_color[4] = {0.f, 0.f, 0.f, 1.f};   // sRGB RGBA (testbed.h:936); training composites on .rgb, the output stage uses all four
+    // view + output-stage state (testbed.h:560-610,904-936)
+    float camera[12] = {1, 0, 0, 0, -1, 0, 0, 0, -1, 0.5f, 0.5f, 2.0f};   // m_camera, column-major mat4x3 (reset_camera)
+    float relative_focal_length[2] = {1.f, 1.f}, screen_center[2] = {0.5f, 0.5f}, zoom = 1.f, scale = 1.5f, up_dir[3] = {0.f, 1.f, 0.f};
+    int fov_axis = 1, training_view = 0;
+    float exposure = 0.f, ground_truth_alpha = 1.f, render_near_distance = 0.f;
+    int color_space = CS_LINEAR, tonemap_curve = TM_IDENTITY, render_mode = RM_SHADE;
+    // tile-sharded inference: render() / render_frame() produce rows y0, y0 + render_row_stride, ... < y1 (default 1: the contiguous band [y0, y1));
+    // with stride = world and y0 = rank every rank gets the same share of every part of the picture, whatever the scene covers
+    int render_row_stride = 1;
+    bool render_ground_truth = false, render_with_lens_distortion = false;
     int loss_type = LOSS_L2, rgb_activation = ACT_LOGISTIC, density_activation = ACT_EXPONENTIAL;
-    bool image_snap_to_pixel_centers = true, image_linear_colors = false, image_stratified = true;
+    bool image_snap_to_pixel_centers = true, image_linear_colors = false;
+    int image_random_mode = IMG_RANDOM_STRATIFIED;   // image.random_mode (testbed.h:881)
     uint64_t seed = 1337;
     uint32_t sampler_lanes_per_ray = 0;   // 0 = automatic; 1 / 2 / 4 / 8 / 32 force a marcher variant (parity tests)
     // generate the NEXT step's rays on a second stream while this step's backward pass and optimizer run (the walk depends on
@@ -177,7 +201,10 @@ private:
     // SDF mode (scratch shared with the image mode)
     DeviceBuffer m_sdf_pos, m_sdf_dist; uint32_t m_sdf_size = 0; bool m_sdf_step_skipped = false; int m_tcnn_loss = TLOSS_L2;
     // render scratch
-    DeviceBuffer m_r_rgba[3], m_r_depth[3], m_r_payload[3], m_r_input, m_r_output, m_r_counters, m_r_scan, m_frame, m_frame_depth, m_accum;
+    DeviceBuffer m_r_rgba[3], m_r_depth[3], m_r_payload[3], m_r_input, m_r_output, m_r_counters, m_r_scan, m_frame, m_frame_depth, m_accum, m_surface, m_r_coarse;
+    TraceCtl* m_trace_host = nullptr; cudaEvent_t m_ev_trace[8] = {};   // host-mapped copies of the tracer's loop control + one event per ring slot
+    // one sample of one row band through the wavefront tracer into m_frame / m_frame_depth (render_nerf, testbed_nerf.cu:2752-2871)
+    void trace_sample(cudaStream_t s, const RenderCamera& cam, int sample, float* frame, float* fdepth);
 };
 
 }  // namespace ngp

@@ -4,6 +4,7 @@
     testbed.set_nerf_dataset(views, aabb_scale=1)       # load_training_data with in-memory views (host buffers)
     testbed.reload_network_from_json(config)
     while testbed.frame(): ...                          # one training step per frame, as scripts/run.py:183
+    testbed.set_camera_to_training_view(i)              # or testbed.camera_matrix / fov / set_nerf_camera_matrix
     image = testbed.render(w, h, spp, linear=True)
 
 All arithmetic runs in libngp_b200.so; torch only provides the CUDA stream and (for data-parallel training) the
@@ -20,10 +21,52 @@ import torch
 from ._lib import TrainingImage, TrainStats, check, lib
 
 
-class TestbedMode(enum.IntEnum):      # python_api.cu:271-277
+class TestbedMode(enum.IntEnum):      # python_api.cu:271-277 (Volume and None exist as values; this library implements Nerf, Sdf, Image)
     Nerf = 0
     Sdf = 1
     Image = 2
+    Volume = 3
+    None_ = 4
+
+
+class GroundTruthRenderMode(enum.IntEnum):   # python_api.cu:282-285
+    Shade = 0
+    Depth = 1
+
+
+class RenderMode(enum.IntEnum):       # python_api.cu:287-297
+    AO = 0
+    Shade = 1
+    Normals = 2
+    Positions = 3
+    Depth = 4
+    Distortion = 5
+    Cost = 6
+    Slice = 7
+
+
+class ColorSpace(enum.IntEnum):       # python_api.cu:338-341
+    Linear = 0
+    SRGB = 1
+
+
+class TonemapCurve(enum.IntEnum):     # python_api.cu:343-348
+    Identity = 0
+    ACES = 1
+    Hable = 2
+    Reinhard = 3
+
+
+class SDFGroundTruthMode(enum.IntEnum):   # python_api.cu:320-324
+    RaytracedMesh = 0
+    SpheretracedMesh = 1
+    SDFBricks = 2
+
+
+class MeshSdfMode(enum.IntEnum):      # python_api.cu:333-337
+    Watertight = 0
+    Raystab = 1
+    PathEscape = 2
 
 
 class LossType(enum.IntEnum):         # python_api.cu:311-319
@@ -32,6 +75,7 @@ class LossType(enum.IntEnum):         # python_api.cu:311-319
     Mape = 2
     Smape = 3
     Huber = 4
+    SmoothL1 = 4      # legacy name of Huber
     LogL1 = 5
     RelativeL2 = 6
 
@@ -43,9 +87,85 @@ class NerfActivation(enum.IntEnum):   # python_api.cu:321-327
     Exponential = 3
 
 
-class LensMode(enum.IntEnum):
+class LensMode(enum.IntEnum):         # python_api.cu:350-357 (this library traces Perspective and OpenCV; the loader rejects the others)
     Perspective = 0
     OpenCV = 1
+    FTheta = 2
+    LatLong = 3
+    OpenCVFisheye = 4
+    Equirectangular = 5
+
+
+class BoundingBox:
+    """pyngp.BoundingBox (python_api.cu:358-377; include/neural-graphics-primitives/bounding_box.cuh:36-242): axis-aligned box, host side"""
+    def __init__(self, a=None, b=None):
+        self.min = np.full(3, np.inf, np.float32) if a is None else np.asarray(a, np.float32).copy()
+        self.max = np.full(3, -np.inf, np.float32) if b is None else np.asarray(b, np.float32).copy()
+
+    def __repr__(self):
+        return f"[min=[{self.min[0]},{self.min[1]},{self.min[2]}], max=[{self.max[0]},{self.max[1]},{self.max[2]}]]"
+
+    def enlarge(self, other):
+        if isinstance(other, BoundingBox):
+            self.min = np.minimum(self.min, other.min); self.max = np.maximum(self.max, other.max)
+        else:
+            q = np.asarray(other, np.float32)
+            self.min = np.minimum(self.min, q); self.max = np.maximum(self.max, q)
+
+    def inflate(self, amount):
+        self.min = self.min - np.float32(amount); self.max = self.max + np.float32(amount)
+
+    def diag(self):
+        return self.max - self.min
+
+    def relative_pos(self, pos):
+        return (np.asarray(pos, np.float32) - self.min) / self.diag()
+
+    def center(self):
+        return np.float32(0.5) * (self.max + self.min)
+
+    def intersection(self, other):
+        return BoundingBox(np.maximum(self.min, other.min), np.minimum(self.max, other.max))
+
+    def is_empty(self):
+        return bool(np.any(self.max < self.min))
+
+    def intersects(self, other):
+        return not self.intersection(other).is_empty()
+
+    def contains(self, p):
+        p = np.asarray(p, np.float32)
+        return bool(np.all(p >= self.min) and np.all(p <= self.max))
+
+    def distance_sq(self, p):
+        p = np.asarray(p, np.float32)
+        d = np.maximum(np.maximum(self.min - p, p - self.max), 0.0)
+        return float(np.dot(d, d))
+
+    def distance(self, p):
+        return float(np.sqrt(self.distance_sq(p)))
+
+    def signed_distance(self, p):
+        q = np.abs(np.asarray(p, np.float32) - self.min) - self.diag()
+        return float(np.linalg.norm(np.maximum(q, 0.0)) + min(float(q.max()), 0.0))
+
+    def ray_intersect(self, pos, direction):
+        """slab test; (tmin, tmax), both FLT_MAX when the ray misses"""
+        pos = np.asarray(pos, np.float32); d = np.asarray(direction, np.float32)
+        miss = (float(np.finfo(np.float32).max),) * 2
+        with np.errstate(divide="ignore", invalid="ignore"):
+            t0, t1 = (self.min - pos) / d, (self.max - pos) / d
+        lo, hi = np.minimum(t0, t1), np.maximum(t0, t1)
+        tmin, tmax = lo[0], hi[0]
+        for k in (1, 2):
+            if tmin > hi[k] or lo[k] > tmax:
+                return miss
+            tmin, tmax = max(tmin, lo[k]), min(tmax, hi[k])
+        return (float(tmin), float(tmax))
+
+    def get_vertices(self):
+        lo, hi = self.min, self.max
+        return [np.array([x, y, z], np.float32) for x in (lo[0], hi[0]) for y in (lo[1], hi[1]) for z in (lo[2], hi[2])]
 
 
 def _stream():
@@ -53,9 +173,14 @@ def _stream():
 
 
 _BOOL_OPTS = {"random_bg_color", "linear_colors", "snap_to_pixel_centers", "train_snap_to_pixel_centers", "shall_train_encoding", "shall_train_network",
-              "image_snap_to_pixel_centers", "image_linear_colors", "image_stratified", "prefetch_rays", "dp_sharded_optimizer", "device_control_law"}
-_FLOAT_OPTS = {"near_distance", "density_grid_decay", "render_min_transmittance", "cone_angle_constant"}
-_INT_OPTS = {"loss_type", "rgb_activation", "density_activation", "seed", "sampler_lanes_per_ray", "prefetch_hits"}
+              "image_snap_to_pixel_centers", "image_linear_colors", "image_stratified", "prefetch_rays", "dp_sharded_optimizer", "device_control_law",
+              "render_ground_truth", "render_with_lens_distortion"}
+_FLOAT_OPTS = {"near_distance", "density_grid_decay", "render_min_transmittance", "cone_angle_constant", "exposure", "zoom", "fov", "ground_truth_alpha",
+               "render_near_distance"}
+_INT_OPTS = {"loss_type", "rgb_activation", "density_activation", "seed", "sampler_lanes_per_ray", "prefetch_hits", "fov_axis"}
+# enum-valued members (python_api.cu:470,522-523,686): reads come back as the enum
+_ENUM_OPTS = {}     # filled below the enum definitions
+_VECTOR_OPTS = {"screen_center": 2, "relative_focal_length": 2, "up_dir": 3, "background_color": 4}
 
 
 class RandomMode(enum.IntEnum):       # python_api.cu:299-305
@@ -63,6 +188,9 @@ class RandomMode(enum.IntEnum):       # python_api.cu:299-305
     Halton = 1
     Sobol = 2
     Stratified = 3
+
+
+_ENUM_OPTS.update({"render_mode": RenderMode, "color_space": ColorSpace, "tonemap_curve": TonemapCurve, "image_random_mode": RandomMode})
 
 
 class _Namespace:
@@ -125,7 +253,7 @@ class Testbed:
         object.__setattr__(self, "_dist", None)
         training = _Namespace(self, {"random_bg_color": "random_bg_color", "loss_type": "loss_type", "near_distance": "near_distance",
                                      "density_grid_decay": "density_grid_decay", "linear_colors": "linear_colors",
-                                     "snap_to_pixel_centers": "train_snap_to_pixel_centers"},
+                                     "snap_to_pixel_centers": "train_snap_to_pixel_centers", "view": "training_view_index"},
                               {"set_image": self.set_training_image, "set_camera_intrinsics": self.set_camera_intrinsics,
                                "set_camera_extrinsics": self.set_camera_extrinsics, "dataset": _Dataset(self),
                                "n_images_for_training": _Lazy(self.n_training_views)})
@@ -151,15 +279,44 @@ class Testbed:
                 pass
             object.__setattr__(self, "_h", None)
 
-    # ---- runtime knobs (def_readwrite members) ----
+    # ---- runtime knobs (def_readwrite members, python_api.cu:452-537) ----
+    def _get_vec(self, name, n):
+        buf = (C.c_float * n)()
+        check(lib().ngp_testbed_get_vector(self._h, name.encode(), buf, n))
+        return np.array(list(buf), np.float32)
+
+    def _set_vec(self, name, values, n):
+        v = np.asarray(values, np.float32).reshape(-1)
+        if v.size != n:
+            raise ValueError(f"{name} takes {n} components")
+        check(lib().ngp_testbed_set_vector(self._h, name.encode(), (C.c_float * n)(*[float(x) for x in v]), n))
+
     def __getattr__(self, name):
-        if name == "background_color":
-            out = []
-            for k in "rgb":
-                v = C.c_double(); check(lib().ngp_testbed_get_option(self._h, f"background_{k}".encode(), C.byref(v))); out.append(v.value)
-            return out
-        if name == "image_random_mode":      # image.random_mode (python_api.cu:686): Stratified <-> image_stratified, everything else plain random
-            return RandomMode.Stratified if self.image_stratified else RandomMode.Random
+        if name in _VECTOR_OPTS:
+            return self._get_vec(name, _VECTOR_OPTS[name])
+        if name in ("aabb", "render_aabb"):
+            v = self._get_vec(name, 6)
+            return BoundingBox(v[:3], v[3:])
+        if name == "camera_matrix":          # m_camera as pybind hands it out: a 3 x 4 array (rows), [R | t]
+            return self._get_vec("camera_matrix", 12).reshape(4, 3).T.copy()
+        if name in ("render_groundtruth",):
+            return self.render_ground_truth
+        if name == "scale":
+            return self.get_option("scale")
+        if name == "training_view_index":    # nerf.training.view (python_api.cu:640): the view set_camera_to_training_view selected
+            return int(self.get_option("training_view"))
+        if name == "fov_xy":                 # focal_length_to_fov per axis (testbed.cu:3818-3820)
+            f = self._get_vec("relative_focal_length", 2)
+            return np.degrees(2.0 * np.arctan(1.0 / (2.0 * f))).astype(np.float32)
+        if name == "view_dir":
+            return self.camera_matrix[:, 2].copy()
+        if name == "view_pos":
+            return self.camera_matrix[:, 3].copy()
+        if name == "look_at":                # testbed.cu:793-795
+            m = self.camera_matrix
+            return m[:, 3] + m[:, 2] * np.float32(self.scale)
+        if name in _ENUM_OPTS:
+            return _ENUM_OPTS[name](int(self.get_option(name)))
         if name in _BOOL_OPTS | _FLOAT_OPTS | _INT_OPTS:
             v = C.c_double()
             check(lib().ngp_testbed_get_option(self._h, name.encode(), C.byref(v)))
@@ -173,15 +330,74 @@ class Testbed:
         return v.value
 
     def __setattr__(self, name, value):
-        if name in _BOOL_OPTS | _FLOAT_OPTS | _INT_OPTS:
+        if name in _BOOL_OPTS | _FLOAT_OPTS | _INT_OPTS | set(_ENUM_OPTS):
             check(lib().ngp_testbed_set_option(self._h, name.encode(), float(value)))
-        elif name == "image_random_mode":
-            self.image_stratified = int(value) == int(RandomMode.Stratified)
-        elif name == "background_color":
-            for k, c in zip("rgb", value):
-                check(lib().ngp_testbed_set_option(self._h, f"background_{k}".encode(), float(c)))
+        elif name == "background_color":     # vec4 in the reference; three components keep the alpha that is set
+            v = list(np.asarray(value, np.float32).reshape(-1))
+            self._set_vec(name, v if len(v) == 4 else v + [float(self.background_color[3])], 4)
+        elif name in _VECTOR_OPTS:
+            self._set_vec(name, value, _VECTOR_OPTS[name])
+        elif name in ("aabb", "render_aabb"):
+            self._set_vec(name, np.concatenate([np.asarray(value.min, np.float32), np.asarray(value.max, np.float32)]), 6)
+        elif name == "camera_matrix":        # 3 x 4 (rows) or 4 x 4, NGP convention
+            m = np.asarray(value, np.float32)
+            if m.shape not in ((3, 4), (4, 4)):
+                raise ValueError("camera_matrix must be a 3x4 or 4x4 matrix")
+            self._set_vec(name, np.ascontiguousarray(m[:3, :4].T).reshape(-1), 12)
+        elif name == "render_groundtruth":
+            self.render_ground_truth = value
+        elif name == "training_view_index":
+            check(lib().ngp_testbed_set_option(self._h, b"training_view", float(int(value))))
+        elif name == "fov_xy":               # fov_to_focal_length per axis (testbed.cu:3822-3824)
+            self._set_vec("relative_focal_length", 0.5 / np.tan(0.5 * np.radians(np.asarray(value, np.float64))), 2)
+        elif name == "scale":                # set_scale (testbed.cu:801-805): the eye moves on the view axis, look_at stays
+            m, old = self.camera_matrix, self.scale
+            look = m[:, 3] + m[:, 2] * np.float32(old)
+            m[:, 3] = (m[:, 3] - look) * np.float32(float(value) / old) + look
+            self.camera_matrix = m
+            check(lib().ngp_testbed_set_option(self._h, b"scale", float(value)))
+        elif name == "look_at":              # set_look_at (testbed.cu:797-799)
+            m = self.camera_matrix
+            m[:, 3] += np.asarray(value, np.float32) - self.look_at
+            self.camera_matrix = m
+        elif name == "view_dir":             # set_view_dir (testbed.cu:807-813)
+            d = np.asarray(value, np.float32); look = self.look_at; m = self.camera_matrix
+            unit = lambda v: v / np.linalg.norm(v)
+            m[:, 0] = unit(np.cross(d, self.up_dir)); m[:, 1] = unit(np.cross(d, m[:, 0])); m[:, 2] = unit(d)
+            self.camera_matrix = m
+            self.look_at = look
         else:
             object.__setattr__(self, name, value)
+
+    # ---- view state (python_api.cu:483-491) ----
+    def reset_camera(self):
+        check(lib().ngp_testbed_reset_camera(self._h))
+
+    def set_nerf_camera_matrix(self, cam):
+        """camera-to-world of the original NeRF convention, 3 x 4 (rows) or 4 x 4; converted with the data set's scale / offset"""
+        m = np.asarray(cam, np.float32)
+        if m.shape not in ((3, 4), (4, 4)):
+            raise ValueError("cam must be a 3x4 or 4x4 matrix")
+        col = np.ascontiguousarray(m[:3, :4].T).reshape(-1)
+        check(lib().ngp_testbed_set_nerf_camera_matrix(self._h, col.ctypes.data_as(C.c_void_p)))
+
+    def set_camera_to_training_view(self, trainview):
+        check(lib().ngp_testbed_set_camera_to_training_view(self._h, int(trainview)))
+
+    def first_training_view(self):
+        self.set_camera_to_training_view(0)
+
+    def last_training_view(self):
+        self.set_camera_to_training_view(self.n_training_views() - 1)
+
+    def previous_training_view(self):
+        self.set_camera_to_training_view(max(self.training_view_index - 1, 0))
+
+    def next_training_view(self):
+        self.set_camera_to_training_view(min(self.training_view_index + 1, self.n_training_views() - 1))
+
+    def reset_accumulation(self, due_to_camera_movement=False, immediate_redraw=True):
+        """every render() call starts from an empty accumulator (render_to_cpu resets it as well, python_api.cu:129): nothing to do"""
 
     # ---- data ----
     def set_nerf_dataset(self, views, aabb_scale=1):
@@ -436,23 +652,45 @@ class Testbed:
         return _wrap(ptr, count, dtype)
 
     # ---- inference ----
-    def render(self, width, height, spp=1, linear=True, camera_matrix=None, focal_length=None, screen_center=(0.5, 0.5), y0=0, y1=None,
-               out=None, return_depth=False):
-        """float32 [rows, W, 4] linear premultiplied RGBA of rows [y0, y1) (python_api.cu:127-205, headless)."""
+    def render(self, width=1920, height=1080, spp=1, linear=True, start_t=-1.0, end_t=-1.0, fps=30.0, shutter_fraction=1.0, *, camera_matrix=None,
+               focal_length=None, screen_center=(0.5, 0.5), y0=0, y1=None, row_stride=1, out=None, return_depth=False):
+        """Testbed.render(width, height, spp, linear, start_t, end_t, fps, shutter_fraction) (python_api.cu:127-205,416-425), headless: the frame
+        the testbed's own camera sees (camera_matrix / fov / fov_axis / zoom / screen_center, set_camera_to_training_view ...), spp samples
+        accumulated, composited over background_color with exposure / tonemap_curve, sRGB-encoded unless `linear`, ground truth overlaid when
+        render_ground_truth is set; float32 [rows, W, 4].  start_t / end_t move the camera along the GUI's camera path, which this library
+        does not have: anything but the default -1 raises.
+
+        Extension (keyword only): an explicit `camera_matrix` (12 floats, mat4x3 column major, NGP convention) with `focal_length` in
+        pixels renders the raw tracer output instead — linear premultiplied RGBA, no background, no tonemapping; `y0` / `y1` / `row_stride`
+        restrict either form to rows y0, y0 + row_stride, ... < y1 (tile-sharded inference: a contiguous band with stride 1, or every
+        world-th row starting at the rank, which balances the ranks whatever the picture shows), `out` may be a CUDA tensor."""
+        if start_t >= 0.0 or end_t >= 0.0:
+            raise RuntimeError("render: camera-path animation (start_t / end_t) is not part of this library (no camera path)")
         y1 = height if y1 is None else y1
         self.sync_inference_params()      # no-op unless the sharded optimizer left other ranks' EMA slices behind (then: collective)
-        cam = (C.c_float * 12)(*[float(x) for x in np.asarray(camera_matrix, np.float32).reshape(-1)])
-        fl = (C.c_float * 2)(*focal_length)
-        sc = (C.c_float * 2)(*screen_center)
-        rows = y1 - y0
+        rows = len(range(y0, y1, int(row_stride)))
         dev_out = out is not None and isinstance(out, torch.Tensor) and out.is_cuda
         if out is None:
             out = np.empty((rows, width, 4), np.float32)
-        depth = np.empty((rows, width), np.float32) if (return_depth and not dev_out) else None
+        elif tuple(out.shape) != (rows, width, 4):
+            raise ValueError(f"render: out must have shape {(rows, width, 4)}")
         optr = C.c_void_p(out.data_ptr()) if isinstance(out, torch.Tensor) else out.ctypes.data_as(C.c_void_p)
-        dptr = depth.ctypes.data_as(C.c_void_p) if depth is not None else None
-        check(lib().ngp_testbed_render(self._h, _stream(), cam, fl, sc, width, height, spp, y0, y1, optr, int(dev_out), dptr))
-        return (out, depth) if return_depth else out
+        check(lib().ngp_testbed_set_option(self._h, b"render_row_stride", float(int(row_stride))))
+        try:
+            if camera_matrix is None:
+                if return_depth:
+                    raise RuntimeError("render: return_depth needs the explicit-camera form")
+                check(lib().ngp_testbed_render_frame(self._h, _stream(), width, height, spp, int(bool(linear)), y0, y1, optr, int(dev_out)))
+                return out
+            cam = (C.c_float * 12)(*[float(x) for x in np.asarray(camera_matrix, np.float32).reshape(-1)])
+            fl = (C.c_float * 2)(*focal_length)
+            sc = (C.c_float * 2)(*screen_center)
+            depth = np.empty((rows, width), np.float32) if (return_depth and not dev_out) else None
+            dptr = depth.ctypes.data_as(C.c_void_p) if depth is not None else None
+            check(lib().ngp_testbed_render(self._h, _stream(), cam, fl, sc, width, height, spp, y0, y1, optr, int(dev_out), dptr))
+            return (out, depth) if return_depth else out
+        finally:
+            check(lib().ngp_testbed_set_option(self._h, b"render_row_stride", 1.0))
 
     def n_training_views(self):
         return lib().ngp_testbed_n_training_views(self._h)
@@ -489,29 +727,41 @@ class Testbed:
         return _wrap(v["device_pixels"], w * h * 4, torch.float32).view(h, w, 4).clone()
 
     def evaluate_training_views(self, view_indices=None, spp=8):
-        """The evaluation protocol of scripts/run.py:208-266, headless: black background, rays through pixel centres,
-        render_min_transmittance 1e-4, spp samples per pixel, each view rendered at its own resolution with its own lens and
-        compared with its ground-truth pixels in sRGB after clipping.  Returns {"psnr", "min_psnr", "max_psnr", "mse", "n"}
-        (psnr = mean of the per-view values, as run.py reports it)."""
+        """The evaluation loop of scripts/run.py:208-266 over the loaded views, statement for statement through the same members a user of
+        the reference calls: black background, rays through pixel centres, render_min_transmittance 1e-4, the ground truth rendered with
+        render_ground_truth + set_camera_to_training_view + render(w, h, 1, True), the model with render(w, h, spp, True), MSE / SSIM
+        (evaluation.compute_error) on the clipped sRGB images.  Frames stay on the device.  Returns {"psnr", "min_psnr", "max_psnr",
+        "psnr_avgmse", "mse", "ssim", "n"} (psnr / ssim = means of the per-view values, as run.py prints them)."""
+        from .evaluation import compute_error, linear_to_srgb, mse2psnr
         idx = list(range(self.n_training_views())) if view_indices is None else list(view_indices)
-        saved = (self.snap_to_pixel_centers, self.render_min_transmittance)
-        self.background_color = [0.0, 0.0, 0.0]
+        saved = (self.background_color, self.snap_to_pixel_centers, self.render_min_transmittance, self.render_ground_truth, self.camera_matrix,
+                 self.relative_focal_length, self.screen_center, self.training_view_index, self.render_with_lens_distortion, self.scale)
+        self.background_color = [0.0, 0.0, 0.0, 1.0]
         self.snap_to_pixel_centers = True
-        self.render_min_transmittance = 1e-4
-
-        def to_srgb(x):
-            return np.where(x < 0.0031308, 12.92 * x, 1.055 * np.power(np.maximum(x, 1e-12), 0.41666) - 0.055)   # common.py linear_to_srgb
-        psnrs, mses = [], []
+        self.nerf.render_min_transmittance = 1e-4
+        psnrs, mses, ssims = [], [], []
         try:
+            meta = self.nerf.training.dataset.metadata
             for i in idx:
-                img = self.render_training_view(i, spp)
-                ref = self.training_view_pixels(i).cpu().numpy()
-                a = np.clip(to_srgb(img[..., :3]), 0.0, 1.0); r = np.clip(to_srgb(ref[..., :3]), 0.0, 1.0)
-                mse = float(((a - r) ** 2).mean())
-                mses.append(mse); psnrs.append(-10.0 * np.log10(max(mse, 1e-12)))
+                w, h = meta[i].resolution
+                buf = torch.empty((2, h, w, 4), dtype=torch.float32, device="cuda")
+                self.render_ground_truth = True
+                self.set_camera_to_training_view(i)
+                ref_image = self.render(w, h, 1, True, out=buf[0])
+                self.render_ground_truth = False
+                image = self.render(w, h, spp, True, out=buf[1])
+                A = linear_to_srgb(image[..., :3]).clamp(0.0, 1.0)
+                R = linear_to_srgb(ref_image[..., :3]).clamp(0.0, 1.0)
+                mse = float(compute_error("MSE", A, R)); ssim = float(compute_error("SSIM", A, R))
+                mses.append(mse); ssims.append(ssim); psnrs.append(float(mse2psnr(max(mse, 1e-12))))
         finally:
-            self.snap_to_pixel_centers, self.render_min_transmittance = saved
-        return {"psnr": float(np.mean(psnrs)), "min_psnr": float(np.min(psnrs)), "max_psnr": float(np.max(psnrs)), "mse": float(np.mean(mses)), "n": len(idx)}
+            (bg, self.snap_to_pixel_centers, self.render_min_transmittance, self.render_ground_truth, cam, rfl, sc, tv, lens, scale) = saved
+            self.background_color = bg; self.camera_matrix = cam; self.relative_focal_length = rfl; self.screen_center = sc
+            self.training_view_index = tv; self.render_with_lens_distortion = lens
+            check(lib().ngp_testbed_set_option(self._h, b"scale", float(scale)))
+        n = max(len(idx), 1)
+        return {"psnr": float(np.sum(psnrs) / n), "min_psnr": float(np.min(psnrs)), "max_psnr": float(np.max(psnrs)),
+                "psnr_avgmse": float(mse2psnr(max(np.sum(mses) / n, 1e-12))), "mse": float(np.sum(mses) / n), "ssim": float(np.sum(ssims) / n), "n": len(idx)}
 
     def compute_image_mse(self, quantize=False):
         v = C.c_float()

@@ -20,6 +20,20 @@ void ref_image_positions(uint64_t seed, uint64_t skip, uint32_t n, int stratify,
         pos[i * 2 + 1] = pos[i * 2 + 1] / (float)size + ((float)y / (float)size);
     }
 }
+// low-discrepancy positions of image.random_mode Halton / Sobol: halton23_kernel (testbed_image.cu:41-46, halton<base> random_val.cuh:293-305) and
+// sobol2_kernel (testbed_image.cu:48-53, ld_random_val_2d random_val.cuh:281-285); base_idx = batch_size * training_step
+void ref_ld_random_val_2d(uint32_t index, uint32_t seed, float* out);   // ngp_ref_nerf.cpp
+static float halton(size_t idx, unsigned base) {
+    float f = 1, result = 0;
+    while (idx > 0) { f /= (float)base; result += f * (float)(idx % base); idx /= base; }
+    return result;
+}
+void ref_image_positions_ld(int mode, uint64_t base_idx, uint32_t seed, uint32_t n, float* pos) {
+    for (uint32_t i = 0; i < n; ++i) {
+        if (mode == 1) { pos[i * 2] = halton(base_idx + i, 2); pos[i * 2 + 1] = halton(base_idx + i, 3); }
+        else ref_ld_random_val_2d((uint32_t)(base_idx + i), seed, pos + (size_t)i * 2);
+    }
+}
 // image: RGBA float32 [H][W][4]; pos in/out (snapped to pixel centres when snap); target [n][3]
 void ref_image_eval(const float* image, int W, int H, uint32_t n, float* pos, float* target, int snap, int linear_colors) {
     auto read_val = [&](int x, int y, float* v) {

@@ -53,6 +53,35 @@ def test_image_batch_matches_oracle(ngp, ref, snap):
     np.testing.assert_allclose(dl.astype(np.float32), rdl.astype(np.float32), rtol=2e-3, atol=1e-8)
 
 
+@pytest.mark.parametrize("mode", ["Halton", "Sobol"])
+def test_image_low_discrepancy_samplers_match_oracle(ngp, ref, mode):
+    """image.random_mode = Halton | Sobol (testbed_image.cu:41-53,227-231): positions of two consecutive steps (the sequences are indexed by
+    batch_size * training_step) bit-exact against the restated generators, targets as for the random modes."""
+    pyngp = importlib.import_module("instant-ngp_b200.pyngp")
+    tb = pyngp.Testbed(pyngp.TestbedMode.Image)
+    img = _image()
+    tb.set_image(img)
+    tb.reload_network_from_json(IMG_CFG)
+    tb.image.random_mode = getattr(pyngp.RandomMode, mode)
+    assert tb.image.random_mode == getattr(pyngp.RandomMode, mode)
+    n = 1 << 12
+    for step in range(2):
+        tb.train(n)
+        pos = tb.debug_tensor("image_pos", torch.float32, n * 2).cpu().numpy().reshape(n, 2)
+        tgt = tb.debug_tensor("image_target", torch.float32, n * 3).cpu().numpy().reshape(n, 3)
+        rpos = np.zeros((n, 2), np.float32)
+        ref.lib().ref_image_positions_ld(ref.i32(int(getattr(pyngp.RandomMode, mode))), ref.u64(n * step), ref.u32(1337), ref.u32(n), ref.P(rpos))
+        raw = rpos.copy()
+        rtgt = np.zeros((n, 3), np.float32)
+        ref.lib().ref_image_eval(ref.P(img), ref.i32(img.shape[1]), ref.i32(img.shape[0]), ref.u32(n), ref.P(rpos), ref.P(rtgt), ref.i32(1), ref.i32(0))
+        assert np.array_equal(pos, rpos)
+        np.testing.assert_allclose(tgt, rtgt, rtol=1e-5, atol=1e-6)
+        assert raw.min() >= 0.0 and raw.max() < 1.0
+        # low discrepancy: a 16 x 16 grid of cells receives n / 256 = 16 points each, give or take (a random draw would spread far wider)
+        counts = np.histogram2d(raw[:, 0], raw[:, 1], bins=16, range=[[0, 1], [0, 1]])[0]
+        assert counts.min() >= 8 and counts.max() <= 24, (counts.min(), counts.max())
+
+
 def test_image_training_converges(ngp):
     pyngp = importlib.import_module("instant-ngp_b200.pyngp")
     tb = pyngp.Testbed(pyngp.TestbedMode.Image)

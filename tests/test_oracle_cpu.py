@@ -260,8 +260,20 @@ def test_pyngp_attribute_tree_matches_the_reference_binding(ngp):
     tb.nerf.rgb_activation = pyngp.NerfActivation.Exponential
     assert tb.random_bg_color is False and tb.near_distance == pytest.approx(0.25) and tb.loss_type == int(pyngp.LossType.Huber)
     assert tb.render_min_transmittance == pytest.approx(1e-4) and tb.nerf.rgb_activation == int(pyngp.NerfActivation.Exponential)
-    tb.background_color = [0.1, 0.2, 0.3]
-    assert tb.background_color == pytest.approx([0.1, 0.2, 0.3])
+    tb.background_color = [0.1, 0.2, 0.3]                  # vec4 in the reference (testbed.h:936); three components keep the alpha
+    assert list(tb.background_color) == pytest.approx([0.1, 0.2, 0.3, 1.0])
+    tb.background_color = [0.0, 0.0, 0.0, 0.5]
+    assert list(tb.background_color) == pytest.approx([0.0, 0.0, 0.0, 0.5])
+    # view state + output stage members scripts/run.py uses (python_api.cu:452-537): host-side state, no device needed
+    assert tb.fov == pytest.approx(50.625, abs=1e-4) and tb.fov_axis == 1 and tb.exposure == 0.0
+    tb.exposure = 1.5; tb.render_mode = pyngp.RenderMode.Depth; tb.tonemap_curve = pyngp.TonemapCurve.ACES; tb.color_space = pyngp.ColorSpace.SRGB
+    assert tb.exposure == 1.5 and tb.render_mode == pyngp.RenderMode.Depth and tb.tonemap_curve == pyngp.TonemapCurve.ACES and tb.color_space == pyngp.ColorSpace.SRGB
+    tb.camera_matrix = [[1, 0, 0, 0.1], [0, 1, 0, 0.2], [0, 0, 1, 0.3]]
+    np.testing.assert_allclose(tb.camera_matrix, [[1, 0, 0, 0.1], [0, 1, 0, 0.2], [0, 0, 1, 0.3]])
+    tb.render_aabb = pyngp.BoundingBox([0.25, 0.25, 0.25], [0.75, 0.75, 0.75])
+    assert np.allclose(tb.render_aabb.min, 0.25) and np.allclose(tb.render_aabb.max, 0.75) and np.allclose(tb.aabb.min, 0.0)
+    with pytest.raises(Exception):
+        tb.set_camera_to_training_view(0)                  # no data set loaded
     assert tb.nerf.training.dataset.n_images == 0 and tb.nerf.training.n_images_for_training == 0
     with pytest.raises(AttributeError):
         tb.nerf.training.optimize_extrinsics = True          # default-off feature outside the path: fails loudly rather than silently
@@ -270,3 +282,14 @@ def test_pyngp_attribute_tree_matches_the_reference_binding(ngp):
     img.image.random_mode = pyngp.RandomMode.Random
     img.image.training.snap_to_pixel_centers = False
     assert img.image_stratified is False and img.image_snap_to_pixel_centers is False
+    for mode in (pyngp.RandomMode.Halton, pyngp.RandomMode.Sobol, pyngp.RandomMode.Stratified):      # testbed_image.cu:41-53: real samplers, not aliases of Random
+        img.image.random_mode = mode
+        assert img.image.random_mode == mode
+
+
+def test_halton_known_values(ref):
+    """halton<2>, halton<3> (random_val.cuh:293-305) known answers: the van der Corput sequences 1/2, 1/4, 3/4, 1/8 ... and 1/3, 2/3, 1/9 ..."""
+    pos = np.zeros((9, 2), np.float32)
+    ref.lib().ref_image_positions_ld(ref.i32(1), ref.u64(0), ref.u32(0), ref.u32(9), ref.P(pos))
+    np.testing.assert_allclose(pos[:, 0], [0, 1 / 2, 1 / 4, 3 / 4, 1 / 8, 5 / 8, 3 / 8, 7 / 8, 1 / 16], rtol=1e-6)
+    np.testing.assert_allclose(pos[:, 1], [0, 1 / 3, 2 / 3, 1 / 9, 4 / 9, 7 / 9, 2 / 9, 5 / 9, 8 / 9], rtol=1e-6)
