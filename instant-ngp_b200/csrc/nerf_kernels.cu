@@ -813,12 +813,14 @@ uint32_t nerf_sampler_lanes_per_ray(uint32_t n_rays) { return n_rays <= 1024 ? 3
 
 void nerf_generate_training_samples(cudaStream_t s, uint32_t n_rays, Aabb aabb, uint32_t max_samples, uint32_t n_rays_total, Pcg32 rng,
                                     uint32_t n_images, const ImageMeta* metas, const uint8_t* bitfield, uint32_t max_mip, bool snap,
-                                    float cone_angle_constant, uint32_t ray_offset, uint32_t n_rays_global, const SamplerBuffers& b) {
+                                    float cone_angle_constant, uint32_t ray_offset, uint32_t n_rays_global, const SamplerBuffers& b, int phase) {
     (void)n_rays_total;
-    NGP_PROFILE_SCOPE(s, "sampler", n_rays);
+    NGP_PROFILE_SCOPE(s, phase == SAMPLER_EMIT ? "sampler_emit" : "sampler", n_rays);
+    const bool walk = phase != SAMPLER_EMIT, emit = phase != SAMPLER_WALK;
     const uint32_t G = b.lanes_per_ray ? b.lanes_per_ray : nerf_sampler_lanes_per_ray(n_rays);
     NGP_CHECK(G == 1 || G == 2 || G == 4 || G == 8 || G == 32, "sampler_lanes_per_ray must be 0 (automatic), 1, 2, 4, 8 or 32");
     NGP_CHECK(!b.dyn || G != 1, "device-side step parameters need a group marcher (lanes per ray > 1)");
+    NGP_CHECK(phase == SAMPLER_ALL || G != 1, "the two-phase sampler needs a group marcher (lanes per ray > 1)");
     uint32_t K = G == 32 ? 1u : 8u / G;                         // 8 candidates per round (32 with a whole warp per ray)
     if (const char* e = getenv("NGP_SAMPLER_K")) K = (uint32_t)atoi(e);
     const bool flat = cone_angle_constant <= 1e-5f && max_mip == 0;
@@ -830,20 +832,23 @@ void nerf_generate_training_samples(cudaStream_t s, uint32_t n_rays, Aabb aabb, 
 #define NGP_SAMPLER_COUNT_F(GG, KK) do { if (flat) NGP_SAMPLER_COUNT(GG, true, KK); else NGP_SAMPLER_COUNT(GG, false, KK); } while (0)
 #define NGP_SAMPLER_WRITE(GG) do { if (flat) sampler_write_group_kernel<GG, true><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, max_samples, bitfield, max_mip, b); \
                                    else sampler_write_group_kernel<GG, false><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, max_samples, bitfield, max_mip, b); } while (0)
-    if (G != 1) {
+    if (G != 1 && walk) {
         sampler_classify_kernel<<<div_round_up(n_rays * 4, 128), 128, 0, s>>>(n_rays, aabb, rng, n_images, metas, snap, cone_angle_constant, ray_offset, n_rays_global, SCAN_BLOCK / G, b);
         NGP_POST_LAUNCH();
     }
     if (G == 1) { if (flat) sampler_count_kernel<true><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, rng, n_images, metas, bitfield, max_mip, snap, cone_angle_constant, ray_offset, n_rays_global, b);
                   else sampler_count_kernel<false><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, rng, n_images, metas, bitfield, max_mip, snap, cone_angle_constant, ray_offset, n_rays_global, b); }
+    else if (!walk) {}
     else if (G == 32) NGP_SAMPLER_COUNT_F(32, 1);
     else if (G == 8) { if (K == 2) NGP_SAMPLER_COUNT_F(8, 2); else NGP_SAMPLER_COUNT_F(8, 1); }
     else if (G == 4) { if (K == 1) NGP_SAMPLER_COUNT_F(4, 1); else if (K == 4) NGP_SAMPLER_COUNT_F(4, 4); else NGP_SAMPLER_COUNT_F(4, 2); }
     else { if (K == 8) NGP_SAMPLER_COUNT_F(2, 8); else NGP_SAMPLER_COUNT_F(2, 4); }
     NGP_POST_LAUNCH();
-    if (b.dyn) scan_block_totals_dyn_kernel<<<1, 1024, 0, s>>>(b.dyn, SCAN_BLOCK / G, b.block_steps, b.block_rays, &b.counters[1]);
+    if (!walk) {}
+    else if (b.dyn) scan_block_totals_dyn_kernel<<<1, 1024, 0, s>>>(b.dyn, SCAN_BLOCK / G, b.block_steps, b.block_rays, &b.counters[1]);
     else scan_block_totals_kernel<<<1, 1024, 0, s>>>(blocks, b.block_steps, b.block_rays, &b.counters[1], nullptr, false);
     NGP_POST_LAUNCH();
+    if (!emit) return;
     if (G == 1) { if (flat) sampler_write_kernel<true><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, max_samples, bitfield, max_mip, b);
                   else sampler_write_kernel<false><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, max_samples, bitfield, max_mip, b); }
     else if (G == 32) NGP_SAMPLER_WRITE(32);

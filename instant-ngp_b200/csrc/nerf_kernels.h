@@ -52,10 +52,14 @@ struct SamplerBuffers {
     const StepParams* dyn;
 };
 uint32_t nerf_sampler_lanes_per_ray(uint32_t n_rays);
+// The group marchers run in two phases that may be launched apart.  WALK (classify, counting walk with its sample log, scan of the block
+// totals) needs the ray count, the rng and the bitfield but NOT max_samples; EMIT (ray compaction under the max_samples cap, log -> coordinates)
+// is the cheap rest.  The testbed starts the WALK of step N + 2 while step N + 1 is still running (Testbed::launch_walk_ahead).
+enum SamplerPhase : int { SAMPLER_ALL = 0, SAMPLER_WALK = 1, SAMPLER_EMIT = 2 };
 void nerf_generate_training_samples(cudaStream_t s, uint32_t n_rays, Aabb aabb, uint32_t max_samples, uint32_t n_rays_total, Pcg32 rng,
                                     uint32_t n_images, const ImageMeta* metas, const uint8_t* bitfield, uint32_t max_mip,
                                     bool snap_to_pixel_centers, float cone_angle_constant, uint32_t ray_offset, uint32_t n_rays_global,
-                                    const SamplerBuffers& b);
+                                    const SamplerBuffers& b, int phase = SAMPLER_ALL);
 
 // ---- loss + compositor + gradient (testbed_nerf.cu:1660-2012) ----
 struct LossConfig {

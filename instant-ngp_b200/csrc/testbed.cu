@@ -42,6 +42,7 @@ Testbed::~Testbed() {
     if (m_ev_prefetch) cudaEventDestroy(m_ev_prefetch);
     if (m_ev_after_mlp) cudaEventDestroy(m_ev_after_mlp);
     if (m_ev_after_loss) cudaEventDestroy(m_ev_after_loss);
+    if (m_ev_walk_ahead) cudaEventDestroy(m_ev_walk_ahead);
     if (m_trace_host) { cudaFreeHost(m_trace_host); for (cudaEvent_t e : m_ev_trace) if (e) cudaEventDestroy(e); }
     if (m_comm_stream) { cudaStreamSynchronize(m_comm_stream); cudaStreamDestroy(m_comm_stream); }
     if (m_copy_stream) { cudaStreamSynchronize(m_copy_stream); cudaStreamDestroy(m_copy_stream); }
@@ -96,7 +97,7 @@ void Testbed::set_nerf_dataset(cudaStream_t s, uint32_t n_images, const HostImag
     if (m_aux_stream) NGP_CUDA_CHECK(cudaStreamSynchronize(m_aux_stream));   // a ray prefetch in flight reads the old images
     if (m_copy_stream) NGP_CUDA_CHECK(cudaStreamSynchronize(m_copy_stream));
     m_copy_pending = false;
-    m_prefetch_valid = false; m_early_prefetch = false; ++m_dataset_version; m_all_images_u8 = true;
+    m_prefetch_valid = false; m_early_prefetch = false; m_walk_ahead_valid = false; ++m_dataset_version; m_all_images_u8 = true;
     for (void* p : m_image_buffers) cudaFree(p);
     m_image_buffers.clear(); m_image_bytes.clear();
     m_frame_has_mask.assign(n_images, false);
@@ -151,13 +152,13 @@ void Testbed::load_nerf_post(cudaStream_t s, int aabb_scale) {
 void Testbed::reset(bool reset_density_grid) {
     NGP_CHECK(m_have_config, "reset: no network config loaded");
     NGP_CUDA_CHECK(cudaDeviceSynchronize());
-    m_prefetch_valid = false; m_early_prefetch = false;
+    m_prefetch_valid = false; m_early_prefetch = false; m_walk_ahead_valid = false;
     reset_network(reset_density_grid);
 }
 
 void Testbed::upload_view_metadata(cudaStream_t s, uint32_t frame_idx) {   // NerfDataset::update_metadata(first, last)
     if (m_aux_stream) NGP_CUDA_CHECK(cudaStreamSynchronize(m_aux_stream));   // a ray prefetch in flight reads the old metadata
-    m_prefetch_valid = false; ++m_dataset_version;
+    m_prefetch_valid = false; m_walk_ahead_valid = false; ++m_dataset_version;
     NGP_CUDA_CHECK(cudaMemcpyAsync(m_metas.as<ImageMeta>() + frame_idx, &m_host_metas[frame_idx], sizeof(ImageMeta), cudaMemcpyHostToDevice, s));
     NGP_CUDA_CHECK(cudaStreamSynchronize(s));
 }
@@ -202,7 +203,7 @@ void Testbed::set_training_image(cudaStream_t s, uint32_t frame_idx, const void*
         content_matters = new_mask || m_frame_has_mask[frame_idx];
         m_frame_has_mask[frame_idx] = new_mask;
     }
-    if (content_matters) { ++m_dataset_version; m_prefetch_valid = false; if (m_aux_stream) NGP_CUDA_CHECK(cudaStreamSynchronize(m_aux_stream)); }
+    if (content_matters) { ++m_dataset_version; m_prefetch_valid = false; m_walk_ahead_valid = false; if (m_aux_stream) NGP_CUDA_CHECK(cudaStreamSynchronize(m_aux_stream)); }
     if (!m_all_images_u8) { NGP_CUDA_CHECK(cudaMemcpyAsync(m_image_buffers[frame_idx], pixels_host, m_image_bytes[frame_idx], cudaMemcpyHostToDevice, s)); return; }
     if (!m_copy_stream) {
         NGP_CUDA_CHECK(cudaStreamCreateWithFlags(&m_copy_stream, cudaStreamNonBlocking));
@@ -362,7 +363,10 @@ void Testbed::train_end(cudaStream_t s, uint32_t measured_override, uint32_t mea
     }
     m_rays_per_batch = (uint32_t)((float)m_rays_per_batch * (float)target / (float)m_measured);
     m_rays_per_batch = std::min((uint32_t)next_multiple(m_rays_per_batch, BATCH_GRANULARITY), 1u << 18);
-    if (m_early_prefetch) {
+    if (m_walk_ahead_valid) {
+        // the counting walk of the next step ran (or is running) with a predicted ray count: right -> only the cheap second phase is left
+        if (!adopt_walk_ahead(target)) launch_ray_prefetch(s, target);
+    } else if (m_early_prefetch) {
         // the next step's sampler is already running (launch_early_prefetch): it is valid if the law evaluated here gives counts within the
         // bounds its grids were sized for (the device evaluated the same arithmetic and generated nothing otherwise)
         m_early_prefetch = false;
@@ -372,6 +376,7 @@ void Testbed::train_end(cudaStream_t s, uint32_t measured_override, uint32_t mea
     } else {
         launch_ray_prefetch(s, target);
     }
+    launch_walk_ahead(target);
     // No host wait for the optimizer: the control law only needed the counters (already here), and everything that consumes
     // the new weights is ordered behind them on `s`.  The host so runs half a step ahead and the device never idles between
     // steps.  Only the loss read-back (every 16th step) has to wait for its reduction.
@@ -449,7 +454,7 @@ void Testbed::launch_ray_prefetch(cudaStream_t s, uint32_t target) {
     if (!prefetch_rays || m_mode != MODE_TB_NERF || !m_all_images_u8) return;
     const uint32_t n_prep_to_skip = std::min(std::max(m_training_step / 16u, 1u), 16u);
     if (m_training_step % n_prep_to_skip == 0) return;      // the next step starts with training_prep_nerf (new bitfield)
-    const uint32_t R = m_rays_per_batch, set = m_training_step & 1u;
+    const uint32_t R = m_rays_per_batch, set = m_training_step % N_SETS;
     const SamplerKey key = sampler_key(R, max_inference_samples(target), target);
     // start beside the hash-grid backward pass and the optimizer (atomics- and HBM-bound, few issue slots used); the fused MLP
     // backward kernel (latency-bound, 8 warps per SM) loses more from sharing its SMs than the overlap wins
@@ -464,12 +469,58 @@ void Testbed::launch_ray_prefetch(cudaStream_t s, uint32_t target) {
     m_prefetch_key = key; m_prefetch_valid = true; m_prefetch_inflight = true;
 }
 
+// Walk-ahead.  With cascades and a cone angle the counting walk is one long dependent chain per ray (fox: 0.8 ms, more than the whole rest of
+// the step) and sits on the cycle loss(N) -> rays_per_batch(N+1) -> walk(N+1) -> forward(N+1) -> loss(N+1): prefetching one step ahead hides
+// it behind the backward pass only.  What the walk of step N+2 needs — the bitfield, the rng, the images and the RAY COUNT — is all known a
+// step early except the ray count, and that is a multiple of 256 which the control law moves rarely once training has settled.  So, called
+// from train_end(N) (m_training_step == N+1 there), this enqueues the walk phase of step N+2 on the auxiliary stream behind the prefetch of
+// step N+1, predicting rays_per_batch(N+2) == rays_per_batch(N+1).  train_end(N+1) knows the true count: equal -> adopt_walk_ahead launches
+// the cheap emit phase with the true sample cap; different (or any other input changed) -> the walk is discarded and the prefetch runs
+// as before.  A third buffer set keeps step N's outputs readable meanwhile.
+void Testbed::launch_walk_ahead(uint32_t target) {
+    if (!walk_ahead || !prefetch_rays || m_mode != MODE_TB_NERF || !m_all_images_u8 || m_comm || m_world != 1) return;
+    if (cone_angle_constant <= 1e-5f && m_max_cascade == 0) return;     // flat marcher: the walk is short and already hidden
+    if (!m_prefetch_valid) return;                                        // nothing in flight for step N+1: no steady state yet
+    const uint32_t s1 = m_training_step, s2 = m_training_step + 1u;       // N+1, N+2
+    const auto refreshes = [](uint32_t step) { const uint32_t skip = std::min(std::max(step / 16u, 1u), 16u); return step % skip == 0; };
+    if (refreshes(s1) || refreshes(s2)) return;                           // a new bitfield would appear under, or after, the walk
+    const uint32_t R = m_rays_per_batch;
+    const uint32_t lanes = sampler_lanes_per_ray ? sampler_lanes_per_ray : nerf_sampler_lanes_per_ray(R);
+    if (lanes == 1) return;
+    if (!m_ev_walk_ahead) NGP_CUDA_CHECK(cudaEventCreateWithFlags(&m_ev_walk_ahead, cudaEventDisableTiming));
+    Pcg32 rng = m_rng; rng.advance();                                     // the rng step N+2 will sample with (advanced once per step, :4127)
+    SamplerKey key = sampler_key(R, 0, target);
+    key.step = s2; key.rng_state = rng.state; key.rng_inc = rng.inc;
+    const SamplerBuffers sb = sampler_buffers(m_aux_stream, s2 % N_SETS, target, R);
+    NGP_CUDA_CHECK(cudaMemsetAsync(sb.counters, 0, 32, m_aux_stream));
+    nerf_generate_training_samples(m_aux_stream, R, aabb, 0, 0, rng, m_n_images, m_metas.as<ImageMeta>(), m_bitfield.as<uint8_t>(), m_max_cascade,
+                                   train_snap_to_pixel_centers, cone_angle_constant, 0, R, sb, SAMPLER_WALK);
+    NGP_CUDA_CHECK(cudaEventRecord(m_ev_walk_ahead, m_aux_stream));
+    m_walk_ahead_key = key; m_walk_ahead_rng = rng; m_walk_ahead_valid = true; m_walk_ahead_inflight = true;
+}
+
+// train_end(N+1): m_training_step == N+2, m_rays_per_batch and the sample cap of step N+2 are known
+bool Testbed::adopt_walk_ahead(uint32_t target) {
+    m_walk_ahead_valid = false;
+    const uint32_t R = m_rays_per_batch, mi = max_inference_samples(target);
+    SamplerKey want = sampler_key(R, 0, target);
+    if (!(want == m_walk_ahead_key) || !prefetch_rays) { ++walk_ahead_misses; return false; }
+    const SamplerKey key = sampler_key(R, mi, target);
+    const SamplerBuffers sb = sampler_buffers(m_aux_stream, m_training_step % N_SETS, target, R);
+    nerf_generate_training_samples(m_aux_stream, R, aabb, mi, 0, m_rng, m_n_images, m_metas.as<ImageMeta>(), m_bitfield.as<uint8_t>(), m_max_cascade,
+                                   train_snap_to_pixel_centers, cone_angle_constant, 0, R, sb, SAMPLER_EMIT);
+    NGP_CUDA_CHECK(cudaEventRecord(m_ev_prefetch, m_aux_stream));
+    m_prefetch_key = key; m_prefetch_valid = true; m_prefetch_inflight = true; m_walk_ahead_inflight = false;   // the emit phase is ordered behind the walk
+    ++walk_ahead_hits;
+    return true;
+}
+
 // The same prefetch, enqueued from train_nerf_step(N) BEFORE the host has seen step N's counters: nerf_control_law (already on `s`, right
 // behind the loss kernel) leaves rays_per_batch / the inference size of step N+1 in device memory and the sampler kernels read them from
 // there; their grids are sized for the bounds.  train_end evaluates the same law on the host and adopts the result if it fits the bounds.
 void Testbed::launch_early_prefetch(cudaStream_t s, uint32_t target, uint32_t rays_bound, uint32_t samples_bound) {
     (void)s;
-    const uint32_t set = (m_training_step + 1u) & 1u;      // m_training_step is still this step's; m_rng has already been advanced
+    const uint32_t set = (m_training_step + 1u) % N_SETS;      // m_training_step is still this step's; m_rng has already been advanced
     static const bool after_mlp = [] { const char* e = getenv("NGP_PREFETCH_AFTER"); return e && std::string(e) == "mlp"; }();
     NGP_CUDA_CHECK(cudaStreamWaitEvent(m_aux_stream, after_mlp ? m_ev_after_mlp : m_ev_after_loss, 0));
     SamplerBuffers sb = sampler_buffers(m_aux_stream, set, target, rays_bound);
@@ -497,7 +548,7 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
     }
     const uint32_t max_samples = target * 16;
     const uint32_t R = m_rays_per_batch, max_rays = 1u << 18;
-    const uint32_t set = m_training_step & 1u;
+    const uint32_t set = m_training_step % N_SETS;
     m_last_set = set;
     const SamplerBuffers sb = sampler_buffers(s, set, target, R);
     LossBuffers lb{};
@@ -518,7 +569,11 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
     const bool prefetched = m_prefetch_valid && m_prefetch_key == key;
     if (m_prefetch_valid || m_prefetch_inflight) NGP_CUDA_CHECK(cudaStreamWaitEvent(s, m_ev_prefetch, 0));   // adopted or stale, it must have left the buffers
     m_prefetch_valid = false; m_prefetch_inflight = false;
-    if (prefetched) ++prefetch_hits; else launch_sampler(s, key, sb);
+    if (prefetched) ++prefetch_hits;
+    else {
+        if (m_walk_ahead_inflight) { NGP_CUDA_CHECK(cudaStreamWaitEvent(s, m_ev_walk_ahead, 0)); m_walk_ahead_inflight = false; }   // a discarded walk may still be writing one of the sets
+        launch_sampler(s, key, sb);
+    }
     NGP_CUDA_CHECK(cudaMemsetAsync(lb.loss, 0, sizeof(float) * R, s));
     const uint32_t ray_offset = m_rank * R, n_rays_global = m_world * R;
     m_nerf_net->inference(s, m_trainer->params, sb.coords, max_inference, mlp_out);   // inference_mixed_precision(.., use_inference_params=false) (:4001)
@@ -540,10 +595,10 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
         const bool next_refreshes_grid = next_step % skip == 0;
         const uint32_t rb = std::min<uint32_t>(1u << 18, (uint32_t)next_multiple((uint64_t)R + R / 2 + BATCH_GRANULARITY, BATCH_GRANULARITY));
         const uint32_t lanes = sampler_lanes_per_ray ? sampler_lanes_per_ray : nerf_sampler_lanes_per_ray(rb);
-        if (device_control_law && prefetch_rays && m_all_images_u8 && !m_comm && m_world == 1 && !next_refreshes_grid && lanes != 1) {
+        if (device_control_law && prefetch_rays && m_all_images_u8 && !m_comm && m_world == 1 && !next_refreshes_grid && lanes != 1 && !m_walk_ahead_valid) {
             early_rays_bound = rb;
             early_samples_bound = std::min<uint32_t>(max_samples, (uint32_t)next_multiple((uint64_t)max_inference + max_inference / 2 + BATCH_GRANULARITY, BATCH_GRANULARITY));
-            StepParams* sp = m_step_params[next_step & 1u].get<StepParams>(1);
+            StepParams* sp = m_step_params[next_step % N_SETS].get<StepParams>(1);
             nerf_control_law(s, sb.counters, R, target, early_rays_bound, early_samples_bound, sp);
             NGP_CUDA_CHECK(cudaEventRecord(m_ev_after_loss, s));
         }

@@ -123,6 +123,15 @@ public:
     // generate the NEXT step's rays on a second stream while this step's backward pass and optimizer run (the walk depends on
     // the occupancy bitfield and the rng only, not on the weights); same samples either way, see launch_ray_prefetch()
     bool prefetch_rays = true;
+    // general marcher (cascades / cone angle: the walk takes longer than the rest of the step): start the counting walk of step N + 2 during
+    // step N + 1, with the ray count PREDICTED to stay what step N + 1 uses (rays_per_batch is a multiple of 256 and moves rarely at steady
+    // state); when the control law then says otherwise the walk is discarded and redone.  Same samples either way.
+    // OFF by default — measured on fox (profiles/r02_fox_walk_ahead_sweep.json, 5000 steps, ms/step off -> on): 8 lanes per ray 1.38 -> 1.65,
+    // 4 lanes 1.62 -> 1.86, 2 lanes 1.99 -> 2.42, 32 lanes 2.01 -> 2.28; 70 % of the predictions hold.  The general marcher is not idle while it
+    // waits on its chain — eight lanes each run the whole chain of a round — so a walk that runs beside every kernel of the step slows those
+    // kernels by as much as it hides (fused MLP forward 0.03 -> 0.5 ms under it).  Kept as an option with its bit-exactness test.
+    bool walk_ahead = false;
+    uint32_t walk_ahead_hits = 0, walk_ahead_misses = 0;   // read-only
     // evaluate the rays_per_batch control law on the device as well and enqueue the next step's sampler before the host has read this
     // step's counters (nerf_kernels.h StepParams); off: the sampler of step N+1 is launched by the host after it has read them.  Same results.
     bool device_control_law = true;
@@ -180,8 +189,9 @@ private:
     uint32_t m_rays_per_batch = 1u << 12, m_n_rays_total = 0, m_measured = 0, m_measured_before = 0;
     // per-step scratch
     // sampler outputs and scratch exist twice: step N reads set N & 1 while the prefetch of step N + 1 fills the other one
-    DeviceBuffer m_numsteps_all[2], m_block_steps[2], m_block_rays[2], m_ray_tmp[2], m_ray_indices[2], m_rays[2], m_numsteps[2], m_coords[2], m_counters[2],
-        m_sample_scratch[2], m_sample_pool[2], m_overflow_slot[2], m_cand_list[2];
+    static constexpr uint32_t N_SETS = 3;   // step N reads set N % 3; N + 1's rays are prefetched into the next and the walk of N + 2 may already fill the third
+    DeviceBuffer m_numsteps_all[N_SETS], m_block_steps[N_SETS], m_block_rays[N_SETS], m_ray_tmp[N_SETS], m_ray_indices[N_SETS], m_rays[N_SETS], m_numsteps[N_SETS],
+        m_coords[N_SETS], m_counters[N_SETS], m_sample_scratch[N_SETS], m_sample_pool[N_SETS], m_overflow_slot[N_SETS], m_cand_list[N_SETS];
     DeviceBuffer m_coarse;   // dilated 16^3 coarse occupancy (ray classification), rebuilt with the bitfield
     DeviceBuffer m_mlp_out, m_dloss, m_coords_compacted, m_loss, m_ray_scratch, m_compacted_numsteps, m_loss_sum, m_t_before;
     cudaStream_t m_aux_stream = nullptr; cudaEvent_t m_ev_counters = nullptr, m_ev_prefetch = nullptr, m_ev_after_mlp = nullptr;
@@ -193,7 +203,11 @@ private:
     cudaStream_t m_copy_stream = nullptr; cudaEvent_t m_ev_copy_gate = nullptr, m_ev_copy_done = nullptr; bool m_copy_pending = false;
     bool m_prefetch_inflight = false;     // a prefetch (adopted or not) may still be writing its buffer set: wait for m_ev_prefetch before reuse
     bool m_early_prefetch = false; uint32_t m_early_rays_bound = 0, m_early_samples_bound = 0, m_early_dataset_version = 0;   // sampler of the next step enqueued from train_nerf_step
-    DeviceBuffer m_step_params[2]; cudaEvent_t m_ev_after_loss = nullptr;
+    DeviceBuffer m_step_params[N_SETS]; cudaEvent_t m_ev_after_loss = nullptr;
+    // walk-ahead (general marcher only, see launch_walk_ahead): the counting walk of step N + 2, started with a PREDICTED ray count
+    bool m_walk_ahead_valid = false, m_walk_ahead_inflight = false; SamplerKey m_walk_ahead_key{}; Pcg32 m_walk_ahead_rng{0}; cudaEvent_t m_ev_walk_ahead = nullptr;
+    void launch_walk_ahead(uint32_t target);
+    bool adopt_walk_ahead(uint32_t target);
     void launch_early_prefetch(cudaStream_t s, uint32_t target, uint32_t rays_bound, uint32_t samples_bound);
     bool m_prefetch_valid = false, m_all_images_u8 = false; SamplerKey m_prefetch_key{}; uint32_t m_dataset_version = 0, m_last_set = 0;
     // image mode

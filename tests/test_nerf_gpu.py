@@ -186,6 +186,48 @@ def test_sampler_with_cascades_and_cone_angle(env, ref, lanes):
     assert ns_gpu.max() > 0
 
 
+@pytest.mark.parametrize("n_warm", [50, 62])
+def test_walk_ahead_is_adopted_and_bit_exact(env, ref, n_warm):
+    """walk_ahead (general marcher): the counting walk of step N+2 runs during step N+1 with a predicted ray count and only the emit phase
+    follows once the control law has spoken.  A step whose rays came that way must equal the oracle bit for bit — same check as
+    test_sampler_with_cascades_and_cone_angle, at step counts where neither that step nor the one before refreshes the occupancy grid —
+    and the per-step traces must be those of a run with walk_ahead off."""
+    pyngp = env["pyngp"]
+    runs = []
+    for wa in (True, False):
+        tb = pyngp.Testbed(pyngp.TestbedMode.Nerf)
+        if wa:
+            tb.walk_ahead = True
+        tb.set_nerf_dataset(env["views"], aabb_scale=4)
+        tb.reload_network_from_json(SMALL_CFG)
+        trace, hits = [], []
+        for _ in range(n_warm):
+            tb.train(BATCH)
+            trace.append((tb.stats.rays_per_batch, tb.stats.measured_batch_size, tb.stats.measured_batch_size_before_compaction))
+            hits.append(tb.walk_ahead_hits)
+        rpb, max_inf, step = _step_and_capture(tb, ref, env, 0)
+        runs.append(trace)
+        if not wa:
+            assert tb.walk_ahead_hits == 0 and tb.walk_ahead is False        # the default
+            continue
+        # the walk of step n_warm is adopted (emit phase launched) at the end of step n_warm - 1
+        assert hits[-1] > hits[-2], (hits[-4:], tb.walk_ahead_misses)
+        aabb = ref.make_aabb((-1.5, -1.5, -1.5), (2.5, 2.5, 2.5))
+        bf = tb.density_grid(1).cpu().numpy()
+        o = ref.generate_training_samples(rpb, aabb, max_inf, 1337, 1 + step * (1 << 32), env["images"], bf, 2, True, 1.0 / 256.0)
+        c = tb.debug_tensor("counters", torch.int32, 4).cpu().numpy().view(np.uint32)
+        assert int(c[0]) == int(o["ray_counter"]) and int(c[1]) == int(o["numsteps_counter"])
+        nr = int(c[0])
+        ref_idx = o["ray_indices"][:nr]; ref_cnt = o["numsteps"][:nr, 0]
+        ns_gpu = tb.debug_tensor("numsteps_all", torch.int32, rpb).cpu().numpy().view(np.uint32)
+        assert np.array_equal(ns_gpu[ref_idx], ref_cnt.astype(np.uint32))
+        assert np.array_equal(tb.debug_tensor("ray_indices", torch.int32, nr).cpu().numpy().view(np.uint32), ref_idx)
+        n_written = int(ref_cnt.sum())
+        gcoords = tb.debug_tensor("coords", torch.float32, n_written * 7).cpu().numpy().reshape(n_written, 7)
+        assert np.array_equal(gcoords.view(np.uint32), o["coords"][:n_written].view(np.uint32))
+    assert runs[0] == runs[1]
+
+
 FOX_LENS = (0.0578421, -0.0805099, -0.000980296, 0.00015575)          # k1, k2, p1, p2 of data/nerf/fox/transforms.json:6-9
 FOX_PRINCIPAL = (554.558 / 1080.0, 965.268 / 1920.0)                  # cx / w, cy / h (:10-13)
 

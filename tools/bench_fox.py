@@ -56,6 +56,8 @@ def main():
     load_s = time.time() - t0
     tb.reload_network_from_json(CONFIGS[args.config])
     tb.sampler_lanes_per_ray = int(os.environ.get("NGP_LANES", "0"))
+    if os.environ.get("NGP_WALK_AHEAD") == "0":
+        tb.walk_ahead = False
     n_views = tb.n_training_views()
     views = list(range(0, n_views, max(n_views // args.eval_views, 1)))[:args.eval_views]
     checkpoints = [c for c in (1000, 5000, 35000) if c <= args.steps] or [args.steps]
@@ -97,6 +99,7 @@ def main():
             ev1.record(); torch.cuda.synchronize()
             out["ms_per_step_prefetch_" + ("on" if prefetch else "off")] = round(ev0.elapsed_time(ev1) / 64, 4)
         out["prefetch_hits"] = tb.prefetch_hits
+        out["walk_ahead"] = {"enabled": bool(tb.walk_ahead), "hits": tb.walk_ahead_hits, "misses": tb.walk_ahead_misses}
         for prefetch in (True, False):
             tb.prefetch_rays = prefetch
             for _ in range(4):
