@@ -298,6 +298,9 @@ int ngp_testbed_compute_image_mse(ngp_testbed_t t, void* stream, int32_t quantiz
  * and optimizer whenever the next step does not refresh the occupancy grid first; results are identical),
  * "device_control_law" (bool, default 1: the rays_per_batch control law is ALSO evaluated on the device so that the next step's rays are
  * generated without waiting for the host to read this step's counters; results are identical),
+ * "optimize_exposure" (bool, default 0), "exposure_l2_reg" (float, default 0), "n_steps_between_cam_updates" (default 16):
+ * nerf.training.optimize_exposure (testbed_nerf.cu:1794,1969-1983,3831-3858) — per-image exposure trained on the device; debug buffers
+ * "cam_exposure" / "cam_exposure_gradient" ([n_images][3] fp32) expose the values,
  * "walk_ahead" (bool, default 0 — measured slower, see csrc/testbed.h; scenes with cascades / a cone angle only: the counting walk of step N+2 is started during step N+1 with the
  * ray count predicted to stay the same, and redone when the control law says otherwise; results are identical; "walk_ahead_hits" /
  * "walk_ahead_misses" count the outcomes, read-only),

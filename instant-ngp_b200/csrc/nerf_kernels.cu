@@ -875,6 +875,16 @@ NGP_D void copy_enc_row(const __half* __restrict__ src, __half* __restrict__ dst
         *reinterpret_cast<uint4*>(dst + blk8_chunk_offset(dst_row, c, width)) = __ldg(reinterpret_cast<const uint4*>(src + blk8_chunk_offset(src_row, c, width)));
 }
 struct LG { V3 loss, grad; };
+NGP_D float pick3(float x, float y, float z, uint32_t c);
+// per-image exposure (optimize_exposure; testbed_nerf.cu:1794,1969-1983): the target is the pixel times 2^exposure; dL/d exposure of a ray is
+// -dL/d prediction (symmetric loss) taken back through the sRGB encoding of the target, times 2^e ln 2, summed per image with atomics
+NGP_D float exposure_scale(float e) { return ngp_expf(0.6931471805599453f * e); }
+NGP_D float srgb_to_linear_derivative(float s) { return s <= 0.04045f ? 1.0f / 12.92f : 2.4f / 1.055f * powf((s + 0.055f) / 1.055f, 1.4f); }   // common_device.cuh:87-93
+NGP_D void accumulate_exposure_gradient(const LossConfig& cfg, uint32_t img, uint32_t c, float grad_c, float target_c, float loss_scale) {
+    float dgt = -grad_c;
+    if (!cfg.linear_colors) dgt /= srgb_to_linear_derivative(target_c);
+    atomicAdd(cfg.exposure_gradient + img * 3 + c, loss_scale * dgt * exposure_scale(cfg.exposure[img * 3 + c]) * 0.6931471805599453f);
+}
 NGP_D LG loss_and_gradient(V3 target, V3 pred, int type) {   // :207-283,1340-1355
     const float d[3] = {pred.x - target.x, pred.y - target.y, pred.z - target.z}, p[3] = {pred.x, pred.y, pred.z}, tg[3] = {target.x, target.y, target.z};
     float l[3], g[3];
@@ -925,18 +935,24 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_forward_kernel(uint32_t n_ray
         // replay the sampler's RNG stream to recover pixel + background colour (:1757-1780)
         const uint32_t ig = ray_offset + sb.ray_indices[i];
         rng.advance((int64_t)((uint64_t)ig * N_MAX_RANDOM_SAMPLES_PER_RAY));
-        const ImageMeta& m = metas[image_idx(ig, n_rays_global, n_images)];
+        const uint32_t img = image_idx(ig, n_rays_global, n_images);
+        const ImageMeta& m = metas[img];
         float uv[2]; random_image_pos_training(rng, m.res, cfg.snap_to_pixel_centers, uv);
         rng.advance(1);   // motionblur_time
         V3 bg = ld3(cfg.background_color);
         if (cfg.random_bg_color) { const float a = rng.next_float(), b = rng.next_float(), c = rng.next_float(); bg = v3(a, b, c); }
         bg = v3(srgb_to_linear(bg.x), srgb_to_linear(bg.y), srgb_to_linear(bg.z));
         float tex[4]; read_rgba(m, uv[0], uv[1], tex);
-        const V3 trgb = v3(tex[0], tex[1], tex[2]); const float ta = tex[3];
+        V3 trgb = v3(tex[0], tex[1], tex[2]); const float ta = tex[3];
+        if (cfg.exposure) trgb = v3(exposure_scale(cfg.exposure[img * 3]) * trgb.x, exposure_scale(cfg.exposure[img * 3 + 1]) * trgb.y, exposure_scale(cfg.exposure[img * 3 + 2]) * trgb.z);
         V3 target;
-        if (cfg.linear_colors) {
+        if (cfg.linear_colors || cfg.color_space == 0) {   // :1801-1808 (m_color_space is Linear unless the caller changed it)
             target = trgb + (1.0f - ta) * bg;
-        } else {
+            if (!cfg.linear_colors) {
+                target = v3(linear_to_srgb(target.x), linear_to_srgb(target.y), linear_to_srgb(target.z));
+                bg = v3(linear_to_srgb(bg.x), linear_to_srgb(bg.y), linear_to_srgb(bg.z));
+            }
+        } else {                                            // color_space SRGB (:1809-1818)
             bg = v3(linear_to_srgb(bg.x), linear_to_srgb(bg.y), linear_to_srgb(bg.z));
             if (ta > 0) {
                 const V3 q = v3(linear_to_srgb(trgb.x / ta), linear_to_srgb(trgb.y / ta), linear_to_srgb(trgb.z / ta));
@@ -945,7 +961,7 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_forward_kernel(uint32_t n_ray
         }
         if (cn == numsteps) rgb_ray = rgb_ray + T * bg;
         float* rs = lb.ray_scratch + (size_t)i * 8;
-        rs[0] = rgb_ray.x; rs[1] = rgb_ray.y; rs[2] = rgb_ray.z; rs[3] = target.x; rs[4] = target.y; rs[5] = target.z;
+        rs[0] = rgb_ray.x; rs[1] = rgb_ray.y; rs[2] = rgb_ray.z; rs[3] = target.x; rs[4] = target.y; rs[5] = target.z; rs[6] = __uint_as_float(img);
         lb.compacted_numsteps[i] = cn;
     }
     uint32_t total;
@@ -1008,6 +1024,10 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_backward_kernel(uint32_t n_ra
         __half2 h[2] = {__floats2half2_rn(g0, g1), __floats2half2_rn(g2, g3)};
         *reinterpret_cast<uint2*>(gout + (size_t)j * 4) = *reinterpret_cast<uint2*>(h);
     }
+    if (cfg.exposure_gradient) {
+#pragma unroll
+        for (uint32_t c = 0; c < 3; ++c) accumulate_exposure_gradient(cfg, __float_as_uint(rs[6]), c, pick3(lg.grad.x, lg.grad.y, lg.grad.z, c), pick3(target.x, target.y, target.z, c), loss_scale);
+    }
 }
 
 // ---- G lanes per ray -------------------------------------------------------------------------------------------------
@@ -1030,7 +1050,7 @@ NGP_D float group_inclusive_scan(float v, uint32_t lane, uint32_t gmask) {
     for (uint32_t o = 1; o < G; o <<= 1) { const float u = __shfl_up_sync(gmask, v, o, G); if (lane >= o) v += u; }
     return v;
 }
-NGP_D float pick3(float x, float y, float z, uint32_t c) { return c == 0 ? x : (c == 1 ? y : z); }
+NGP_D float pick3(float x, float y, float z, uint32_t c) { return c == 0 ? x : (c == 1 ? y : z); }   // (declared above)
 
 template <uint32_t G>
 __global__ void __launch_bounds__(SCAN_BLOCK) loss_forward_group_kernel(uint32_t n_rays, Pcg32 rng, LossConfig cfg, uint32_t n_images, const ImageMeta* __restrict__ metas,
@@ -1084,7 +1104,8 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_forward_group_kernel(uint32_t
         // replay the sampler's RNG stream to recover pixel + background colour (:1757-1780); uniform across the group
         const uint32_t ig = ray_offset + sb.ray_indices[i];
         rng.advance((int64_t)((uint64_t)ig * N_MAX_RANDOM_SAMPLES_PER_RAY));
-        const ImageMeta& m = metas[image_idx(ig, n_rays_global, n_images)];
+        const uint32_t img = image_idx(ig, n_rays_global, n_images);
+        const ImageMeta& m = metas[img];
         float uv[2]; random_image_pos_training(rng, m.res, cfg.snap_to_pixel_centers, uv);
         rng.advance(1);
         V3 bg3 = ld3(cfg.background_color);
@@ -1092,11 +1113,13 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_forward_group_kernel(uint32_t
         float tex[4]; read_rgba(m, uv[0], uv[1], tex);
         if (lane < 3) {   // one colour channel per lane: the transcendental conversions run once per warp instruction, not three times
             float bg = srgb_to_linear(pick3(bg3.x, bg3.y, bg3.z, lane));
-            const float trgb = pick3(tex[0], tex[1], tex[2], lane), ta = tex[3];
+            float trgb = pick3(tex[0], tex[1], tex[2], lane); const float ta = tex[3];
+            if (cfg.exposure) trgb = exposure_scale(cfg.exposure[img * 3 + lane]) * trgb;
             float target;
-            if (cfg.linear_colors) {
+            if (cfg.linear_colors || cfg.color_space == 0) {   // :1801-1808
                 target = trgb + (1.0f - ta) * bg;
-            } else {
+                if (!cfg.linear_colors) { target = linear_to_srgb(target); bg = linear_to_srgb(bg); }
+            } else {                                            // color_space SRGB (:1809-1818)
                 bg = linear_to_srgb(bg);
                 target = ta > 0 ? linear_to_srgb(trgb / ta) * ta + (1.0f - ta) * bg : bg;
             }
@@ -1104,6 +1127,7 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_forward_group_kernel(uint32_t
             if (cn == numsteps) ray_c = ray_c + T * bg;
             float* rs = lb.ray_scratch + (size_t)i * 8;
             rs[lane] = ray_c; rs[3 + lane] = target;
+            if (lane == 0) rs[6] = __uint_as_float(img);
         }
         if (lane == 0) lb.compacted_numsteps[i] = cn;
     }
@@ -1183,6 +1207,47 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_backward_group_kernel(uint32_
             *reinterpret_cast<uint2*>(gout + (size_t)j * 4) = *reinterpret_cast<uint2*>(h);
         }
     }
+    if (cfg.exposure_gradient && lane < 3)   // one channel per lane
+        accumulate_exposure_gradient(cfg, __float_as_uint(rs[6]), lane, pick3(lg.grad.x, lg.grad.y, lg.grad.z, lane), pick3(target.x, target.y, target.z, lane), loss_scale);
+}
+
+// one block: the image count is tens to a few thousand, the work is 3 * n_images Adam updates and three means
+__global__ void __launch_bounds__(256) exposure_step_kernel(uint32_t n_images, const float* __restrict__ gradient, float* __restrict__ exposure, float* __restrict__ m1,
+                                                             float* __restrict__ m2, float actual_lr, float l2_reg, float scale) {
+    __shared__ float sums[3][8];
+    float local[3] = {0.f, 0.f, 0.f};
+    for (uint32_t i = threadIdx.x; i < n_images; i += blockDim.x) {
+#pragma unroll
+        for (uint32_t c = 0; c < 3; ++c) {
+            const uint32_t k = i * 3 + c;
+            const float g = gradient[k] * scale + exposure[k] * l2_reg;
+            const float a = 0.9f * m1[k] + (1.0f - 0.9f) * g, b = 0.99f * m2[k] + (1.0f - 0.99f) * g * g;
+            m1[k] = a; m2[k] = b;
+            const float v = exposure[k] - actual_lr * a / (sqrtf(b) + 1e-8f);
+            exposure[k] = v; local[c] += v;
+        }
+    }
+#pragma unroll
+    for (uint32_t c = 0; c < 3; ++c) {
+        float v = local[c];
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31u) == 0) sums[c][threadIdx.x >> 5] = v;
+    }
+    __syncthreads();
+    float mean[3];
+#pragma unroll
+    for (uint32_t c = 0; c < 3; ++c) { float t = 0.f; for (int w = 0; w < 8; ++w) t += sums[c][w]; mean[c] = t / (float)n_images; }
+    for (uint32_t i = threadIdx.x; i < n_images; i += blockDim.x) {      // renormalise: exposures are relative to their mean
+#pragma unroll
+        for (uint32_t c = 0; c < 3; ++c) exposure[i * 3 + c] -= mean[c];
+    }
+}
+void nerf_exposure_step(cudaStream_t s, uint32_t n_images, const float* gradient, float* exposure, float* first_moment, float* second_moment, uint32_t iter,
+                        float learning_rate, float l2_reg, float per_camera_loss_scale) {
+    if (!n_images) return;
+    const float actual_lr = learning_rate * std::sqrt(1.0f - std::pow(0.99f, (float)iter)) / (1.0f - std::pow(0.9f, (float)iter));
+    exposure_step_kernel<<<1, 256, 0, s>>>(n_images, gradient, exposure, first_moment, second_moment, actual_lr, l2_reg, per_camera_loss_scale);
+    NGP_POST_LAUNCH();
 }
 
 void nerf_compute_loss(cudaStream_t s, uint32_t n_rays, Aabb aabb, uint32_t n_rays_total, Pcg32 rng, uint32_t max_compacted, const LossConfig& cfg,

@@ -68,6 +68,9 @@ struct LossConfig {
     float background_color[3];
     float loss_scale;       // LOSS_SCALE; divided by the (global) ray count inside
     float near_distance;
+    int color_space;                // Testbed::m_color_space: 0 Linear (default) / 1 SRGB selects the target formula (testbed_nerf.cu:1801-1818)
+    const float* exposure;          // [n_images][3] per-image exposure in stops (cam_exposure_gpu) or nullptr = all zero (scale exactly 1)
+    float* exposure_gradient;       // [n_images][3] accumulated dL/d exposure (optimize_exposure, :1969-1983) or nullptr
 };
 struct LossBuffers {
     const __half* network_output;   // [*][4]
@@ -84,6 +87,10 @@ struct LossBuffers {
 void nerf_compute_loss(cudaStream_t s, uint32_t n_rays, Aabb aabb, uint32_t n_rays_total, Pcg32 rng, uint32_t max_samples_compacted,
                        const LossConfig& cfg, uint32_t n_images, const ImageMeta* metas, const float* mean_density_dev,
                        uint32_t ray_offset, uint32_t n_rays_global, const SamplerBuffers& sb, const LossBuffers& lb);
+// optimize_exposure (testbed_nerf.cu:3831-3858), on the device: one AdamOptimizer<vec3> step per image (adam_optimizer.h:143-150: lr sqrt(1 - b2^t) / (1 - b1^t),
+// beta1 0.9, beta2 0.99, epsilon 1e-8) on gradient * per_camera_loss_scale + l2_reg * exposure, then the mean over the images is subtracted
+void nerf_exposure_step(cudaStream_t s, uint32_t n_images, const float* gradient, float* exposure, float* first_moment, float* second_moment, uint32_t iter,
+                        float learning_rate, float l2_reg, float per_camera_loss_scale);
 // fill_rollover_and_rescale + fill_rollover (tcnn; testbed_nerf.cu:4061-4069) on dL [n_target][4] fp16 and coords [n_target][7]
 void nerf_fill_rollover(cudaStream_t s, uint32_t n_target, const uint32_t* n_input_dev, __half* dloss, float* coords, __half* enc = nullptr, uint32_t enc_width = 0);
 // sum of loss[0..n) -> *out_dev (deterministic)

@@ -96,6 +96,7 @@ void Testbed::set_nerf_dataset(cudaStream_t s, uint32_t n_images, const HostImag
     NGP_CHECK(aabb_scale <= (1 << (NERF_CASCADES - 1)), "NeRF dataset must have `aabb_scale <= 128`");
     if (m_aux_stream) NGP_CUDA_CHECK(cudaStreamSynchronize(m_aux_stream));   // a ray prefetch in flight reads the old images
     if (m_copy_stream) NGP_CUDA_CHECK(cudaStreamSynchronize(m_copy_stream));
+    m_cam_exposure_n = 0; m_n_steps_since_cam_update = 0;   // load_nerf_post (testbed_nerf.cu:3036-3046): fresh exposure optimisers
     m_copy_pending = false;
     m_prefetch_valid = false; m_early_prefetch = false; m_walk_ahead_valid = false; ++m_dataset_version; m_all_images_u8 = true;
     for (void* p : m_image_buffers) cudaFree(p);
@@ -153,6 +154,7 @@ void Testbed::reset(bool reset_density_grid) {
     NGP_CHECK(m_have_config, "reset: no network config loaded");
     NGP_CUDA_CHECK(cudaDeviceSynchronize());
     m_prefetch_valid = false; m_early_prefetch = false; m_walk_ahead_valid = false;
+    m_cam_exposure_n = 0; m_n_steps_since_cam_update = 0;   // reset_network -> reset_camera_extrinsics (testbed.cu:3921): exposure optimisers start over
     reset_network(reset_density_grid);
 }
 
@@ -363,6 +365,14 @@ void Testbed::train_end(cudaStream_t s, uint32_t measured_override, uint32_t mea
     }
     m_rays_per_batch = (uint32_t)((float)m_rays_per_batch * (float)target / (float)m_measured);
     m_rays_per_batch = std::min((uint32_t)next_multiple(m_rays_per_batch, BATCH_GRANULARITY), 1u << 18);
+    // camera-side optimisers (testbed_nerf.cu:3754-3861; of those this library trains the exposure)
+    m_n_steps_since_cam_update += 1;
+    if (optimize_exposure && m_cam_exposure_n == m_n_images && m_n_steps_since_cam_update >= n_steps_between_cam_updates) {
+        const float per_camera_loss_scale = (float)m_n_images / LOSS_SCALE / (float)n_steps_between_cam_updates;
+        nerf_exposure_step(s, m_n_images, m_cam_exposure_grad.as<float>(), m_cam_exposure.as<float>(), m_cam_exposure_m1.as<float>(), m_cam_exposure_m2.as<float>(),
+                           ++m_cam_exposure_iter, m_trainer->opt.current_lr, exposure_l2_reg, per_camera_loss_scale);
+        m_n_steps_since_cam_update = 0;
+    }
     if (m_walk_ahead_valid) {
         // the counting walk of the next step ran (or is running) with a predicted ray count: right -> only the cheap second phase is left
         if (!adopt_walk_ahead(target)) launch_ray_prefetch(s, target);
@@ -467,6 +477,13 @@ void Testbed::launch_ray_prefetch(cudaStream_t s, uint32_t target) {
     launch_sampler(m_aux_stream, key, sb);
     NGP_CUDA_CHECK(cudaEventRecord(m_ev_prefetch, m_aux_stream));
     m_prefetch_key = key; m_prefetch_valid = true; m_prefetch_inflight = true;
+}
+
+void Testbed::ensure_cam_exposure(cudaStream_t s) {
+    if (m_cam_exposure_n == m_n_images) return;
+    for (DeviceBuffer* b : {&m_cam_exposure, &m_cam_exposure_grad, &m_cam_exposure_m1, &m_cam_exposure_m2})
+        NGP_CUDA_CHECK(cudaMemsetAsync(b->get<float>((size_t)m_n_images * 3), 0, (size_t)m_n_images * 12, s));
+    m_cam_exposure_iter = 0; m_cam_exposure_n = m_n_images;
 }
 
 // Walk-ahead.  With cascades and a cone angle the counting walk is one long dependent chain per ray (fox: 0.8 ms, more than the whole rest of
@@ -582,7 +599,15 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
     lc.loss_type = loss_type; lc.rgb_activation = rgb_activation; lc.density_activation = density_activation;
     lc.random_bg_color = random_bg_color; lc.linear_colors = linear_colors; lc.snap_to_pixel_centers = train_snap_to_pixel_centers;
     memcpy(lc.background_color, background_color, sizeof(lc.background_color));
-    lc.loss_scale = LOSS_SCALE; lc.near_distance = near_distance;
+    lc.loss_scale = LOSS_SCALE; lc.near_distance = near_distance; lc.color_space = color_space;
+    if (optimize_exposure) ensure_cam_exposure(s);
+    if (m_cam_exposure_n == m_n_images && m_n_images) {   // trained (now or earlier): the targets carry the per-image exposure; gradients only while it is being optimised
+        lc.exposure = m_cam_exposure.as<float>();
+        if (optimize_exposure) {
+            lc.exposure_gradient = m_cam_exposure_grad.as<float>();
+            if (m_n_steps_since_cam_update == 0) NGP_CUDA_CHECK(cudaMemsetAsync(lc.exposure_gradient, 0, (size_t)m_n_images * 12, s));   // :3641-3644
+        }
+    }
     lb.enc_in = m_nerf_net->last_inference_encoding();   // written by inference() just above
     if (m_copy_pending) { NGP_CUDA_CHECK(cudaStreamWaitEvent(s, m_ev_copy_done, 0)); m_copy_pending = false; }   // uploaded view(s), see set_training_image
     nerf_compute_loss(s, R, aabb, n_rays_total, m_rng, target, lc, m_n_images, m_metas.as<ImageMeta>(), m_mean.as<float>(), ray_offset, n_rays_global, sb, lb);
@@ -876,7 +901,13 @@ void Testbed::render_frame(cudaStream_t s, int w, int h, int spp, bool to_srgb, 
         NGP_CHECK(training_view >= 0 && training_view < (int)m_n_images, "render_ground_truth: no training view selected");
         const ImageMeta& m = m_host_metas[training_view];
         NGP_CHECK(m.pixels, "render_ground_truth: the training view has no pixels (metadata restored from a snapshot)");
-        const float e3[3] = {exposure, exposure, exposure};   // + cam_exposure[view], which this library does not optimise (zero)
+        float e3[3] = {exposure, exposure, exposure};   // + cam_exposure[view] (testbed.cu:4726)
+        if (m_cam_exposure_n == m_n_images && m_n_images) {
+            float ce[3];
+            NGP_CUDA_CHECK(cudaMemcpyAsync(ce, m_cam_exposure.as<float>() + (size_t)training_view * 3, 12, cudaMemcpyDeviceToHost, s));
+            NGP_CUDA_CHECK(cudaStreamSynchronize(s));
+            for (int k = 0; k < 3; ++k) e3[k] += ce[k];
+        }
         const float centre[2] = {0.5f, 0.5f};
         frame_overlay_image(s, w, h, y0, y1, ground_truth_alpha, e3, background_color, out_cs, m.pixels, m.data_type, m.res, tonemap_curve, color_space, fov_axis, zoom,
                             centre, surface);
@@ -892,7 +923,7 @@ void Testbed::debug_buffer(const std::string& name, void** ptr, uint64_t* bytes)
     const E table[] = {{"coords", &m_coords[k]}, {"numsteps", &m_numsteps[k]}, {"ray_indices", &m_ray_indices[k]}, {"rays", &m_rays[k]}, {"counters", &m_counters[k]},
                        {"mlp_out", &m_mlp_out}, {"dloss", &m_dloss}, {"coords_compacted", &m_coords_compacted}, {"loss", &m_loss},
                        {"grid_pos", &m_grid_pos}, {"grid_idx", &m_grid_idx}, {"grid_out", &m_grid_out}, {"density_grid_tmp", &m_density_grid_tmp},
-                       {"mean_density", &m_mean}, {"numsteps_all", &m_numsteps_all[k]}, {"image_pos", &m_img_pos}, {"image_target", &m_img_target},
+                       {"mean_density", &m_mean}, {"cam_exposure", &m_cam_exposure}, {"cam_exposure_gradient", &m_cam_exposure_grad}, {"numsteps_all", &m_numsteps_all[k]}, {"image_pos", &m_img_pos}, {"image_target", &m_img_target},
                        {"image_out", &m_img_out}, {"image_dl", &m_img_dl}, {"sdf_positions", &m_sdf_pos}, {"sdf_distances", &m_sdf_dist}};
     for (const E& e : table) if (name == e.n) { *ptr = e.b->ptr; *bytes = e.b->bytes; return; }
     throw Error("debug_buffer: unknown buffer '" + name + "'");

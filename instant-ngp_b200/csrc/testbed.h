@@ -123,6 +123,9 @@ public:
     // generate the NEXT step's rays on a second stream while this step's backward pass and optimizer run (the walk depends on
     // the occupancy bitfield and the rng only, not on the weights); same samples either way, see launch_ray_prefetch()
     bool prefetch_rays = true;
+    // nerf.training.optimize_exposure / exposure_l2_reg / n_steps_between_cam_updates (testbed.h:712,727,730): per-image exposure (stops) trained
+    // with its own Adam every n_steps_between_cam_updates steps from the gradient the loss kernel accumulates; everything stays on the device
+    bool optimize_exposure = false; float exposure_l2_reg = 0.0f; uint32_t n_steps_between_cam_updates = 16;
     // general marcher (cascades / cone angle: the walk takes longer than the rest of the step): start the counting walk of step N + 2 during
     // step N + 1, with the ray count PREDICTED to stay what step N + 1 uses (rays_per_batch is a multiple of 256 and moves rarely at steady
     // state); when the control law then says otherwise the walk is discarded and redone.  Same samples either way.
@@ -210,6 +213,8 @@ private:
     bool adopt_walk_ahead(uint32_t target);
     void launch_early_prefetch(cudaStream_t s, uint32_t target, uint32_t rays_bound, uint32_t samples_bound);
     bool m_prefetch_valid = false, m_all_images_u8 = false; SamplerKey m_prefetch_key{}; uint32_t m_dataset_version = 0, m_last_set = 0;
+    DeviceBuffer m_cam_exposure, m_cam_exposure_grad, m_cam_exposure_m1, m_cam_exposure_m2; uint32_t m_cam_exposure_iter = 0, m_n_steps_since_cam_update = 0, m_cam_exposure_n = 0;
+    void ensure_cam_exposure(cudaStream_t s);
     // image mode
     DeviceBuffer m_image; int m_image_w = 0, m_image_h = 0; DeviceBuffer m_img_pos, m_img_target, m_img_out, m_img_dl, m_img_loss;
     // SDF mode (scratch shared with the image mode)

@@ -174,10 +174,10 @@ def _stream():
 
 _BOOL_OPTS = {"random_bg_color", "linear_colors", "snap_to_pixel_centers", "train_snap_to_pixel_centers", "shall_train_encoding", "shall_train_network",
               "image_snap_to_pixel_centers", "image_linear_colors", "image_stratified", "prefetch_rays", "dp_sharded_optimizer", "device_control_law",
-              "render_ground_truth", "render_with_lens_distortion", "walk_ahead"}
+              "render_ground_truth", "render_with_lens_distortion", "walk_ahead", "optimize_exposure"}
 _FLOAT_OPTS = {"near_distance", "density_grid_decay", "render_min_transmittance", "cone_angle_constant", "exposure", "zoom", "fov", "ground_truth_alpha",
-               "render_near_distance"}
-_INT_OPTS = {"loss_type", "rgb_activation", "density_activation", "seed", "sampler_lanes_per_ray", "prefetch_hits", "fov_axis", "walk_ahead_hits", "walk_ahead_misses"}
+               "render_near_distance", "exposure_l2_reg"}
+_INT_OPTS = {"loss_type", "rgb_activation", "density_activation", "seed", "sampler_lanes_per_ray", "prefetch_hits", "fov_axis", "walk_ahead_hits", "walk_ahead_misses", "n_steps_between_cam_updates"}
 # enum-valued members (python_api.cu:470,522-523,686): reads come back as the enum
 _ENUM_OPTS = {}     # filled below the enum definitions
 _VECTOR_OPTS = {"screen_center": 2, "relative_focal_length": 2, "up_dir": 3, "background_color": 4}
@@ -253,7 +253,9 @@ class Testbed:
         object.__setattr__(self, "_dist", None)
         training = _Namespace(self, {"random_bg_color": "random_bg_color", "loss_type": "loss_type", "near_distance": "near_distance",
                                      "density_grid_decay": "density_grid_decay", "linear_colors": "linear_colors",
-                                     "snap_to_pixel_centers": "train_snap_to_pixel_centers", "view": "training_view_index"},
+                                     "snap_to_pixel_centers": "train_snap_to_pixel_centers", "view": "training_view_index",
+                                     "optimize_exposure": "optimize_exposure", "exposure_l2_reg": "exposure_l2_reg",
+                                     "n_steps_between_cam_updates": "n_steps_between_cam_updates"},
                               {"set_image": self.set_training_image, "set_camera_intrinsics": self.set_camera_intrinsics,
                                "set_camera_extrinsics": self.set_camera_extrinsics, "dataset": _Dataset(self),
                                "n_images_for_training": _Lazy(self.n_training_views)})

@@ -102,6 +102,7 @@ static inline void ld_random_pixel_offset(uint32_t spp, float* off) {   // rando
 
 // ---- colour (common_device.cuh:75-121) ----
 extern "C" float ref_srgb_to_linear(float s) { return s <= 0.04045f ? s / 12.92f : powf((s + 0.055f) / 1.055f, 2.4f); }
+static float srgb_to_linear_derivative(float s) { return s <= 0.04045f ? 1.0f / 12.92f : 2.4f / 1.055f * powf((s + 0.055f) / 1.055f, 1.4f); }   // common_device.cuh:87-93
 extern "C" float ref_linear_to_srgb(float l) { return l < 0.0031308f ? 12.92f * l : 1.055f * powf(l, 0.41666f) - 0.055f; }
 
 // ---- stepping (testbed_nerf.cu:124-184) ----
@@ -551,13 +552,20 @@ extern "C" void ref_compute_loss(uint32_t n_rays, const RefAabb* aabb, uint32_t 
         bg = v3(ref_srgb_to_linear(bg.x), ref_srgb_to_linear(bg.y), ref_srgb_to_linear(bg.z));
         float tex[4]; read_rgba(m, uv, tex);
         V3 trgb = v3(tex[0], tex[1], tex[2]); float ta = tex[3];
+        // exposure_scale = exp(ln2 * exposure[img]) (:1794); NULL = the all-zero default, scale exactly 1
+        V3 es = v3(1.f, 1.f, 1.f);
+        if (cfg->exposure) es = v3(m_expf(0.6931471805599453f * cfg->exposure[img * 3]), m_expf(0.6931471805599453f * cfg->exposure[img * 3 + 1]), m_expf(0.6931471805599453f * cfg->exposure[img * 3 + 2]));
         V3 target;
-        if (cfg->linear_colors) {   // train_in_linear_colors (:1801-1808); color_space is SRGB by default
-            target = trgb + (1.0f - ta) * bg;
-        } else {
+        if (cfg->linear_colors || cfg->color_space == 0) {   // :1801-1808 (m_color_space is Linear by default, testbed.h:907)
+            target = v3(es.x * trgb.x, es.y * trgb.y, es.z * trgb.z) + (1.0f - ta) * bg;
+            if (!cfg->linear_colors) {
+                target = v3(ref_linear_to_srgb(target.x), ref_linear_to_srgb(target.y), ref_linear_to_srgb(target.z));
+                bg = v3(ref_linear_to_srgb(bg.x), ref_linear_to_srgb(bg.y), ref_linear_to_srgb(bg.z));
+            }
+        } else {                                              // color_space SRGB (:1809-1818)
             bg = v3(ref_linear_to_srgb(bg.x), ref_linear_to_srgb(bg.y), ref_linear_to_srgb(bg.z));
             if (ta > 0) {
-                V3 q = v3(ref_linear_to_srgb(trgb.x / ta), ref_linear_to_srgb(trgb.y / ta), ref_linear_to_srgb(trgb.z / ta));
+                V3 q = v3(ref_linear_to_srgb(es.x * trgb.x / ta), ref_linear_to_srgb(es.y * trgb.y / ta), ref_linear_to_srgb(es.z * trgb.z / ta));
                 target = q * ta + (1.0f - ta) * bg;
             } else target = bg;
         }
@@ -601,6 +609,13 @@ extern "C" void ref_compute_loss(uint32_t n_rays, const RefAabb* aabb, uint32_t 
             float g3 = loss_scale * dl_dmlp + (o3 < 0.0f ? -output_l1_reg_density : 0.0f) + (o3 > -10.0f && depth < cfg->near_distance ? 1e-4f : 0.0f);
             uint16_t* go = out->dloss_doutput + (size_t)(cbase + j) * 4;
             go[0] = f2h(g0); go[1] = f2h(g1); go[2] = f2h(g2); go[3] = f2h(g3);
+        }
+        if (cfg->exposure_gradient) {   // :1969-1983 (assumes a symmetric loss; uv_pdf = 1 without the error-map CDFs)
+            V3 dgt = v3(-lg.grad.x, -lg.grad.y, -lg.grad.z);
+            if (!cfg->linear_colors) dgt = v3(dgt.x / srgb_to_linear_derivative(target.x), dgt.y / srgb_to_linear_derivative(target.y), dgt.z / srgb_to_linear_derivative(target.z));
+            cfg->exposure_gradient[img * 3 + 0] += loss_scale * dgt.x * es.x * 0.6931471805599453f;
+            cfg->exposure_gradient[img * 3 + 1] += loss_scale * dgt.y * es.y * 0.6931471805599453f;
+            cfg->exposure_gradient[img * 3 + 2] += loss_scale * dgt.z * es.z * 0.6931471805599453f;
         }
     }
     out->compacted_counter = compacted_counter;

@@ -91,6 +91,9 @@ typedef struct RefLossCfg {
     float loss_scale;          // LOSS_SCALE (128), divided by n_rays inside (testbed_nerf.cu:1903)
     float near_distance;
     float mean_density;        // *mean_density_ptr
+    int color_space;           // Testbed::m_color_space (testbed.h:907): 0 Linear (default), 1 SRGB — selects the target formula (testbed_nerf.cu:1801-1818)
+    const float* exposure;     // [n_images][3] per-image exposure in stops (cam_exposure_gpu) or NULL = all zero
+    float* exposure_gradient;  // [n_images][3] accumulated dL/d exposure (optimize_exposure, :1969-1983) or NULL
 } RefLossCfg;
 typedef struct RefLossOut {
     uint16_t* dloss_doutput;     // [max_compacted][4] fp16

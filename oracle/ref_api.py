@@ -43,7 +43,7 @@ class SamplerOut(C.Structure):
 
 class LossCfg(C.Structure):
     _fields_ = [("loss_type", i32), ("rgb_activation", i32), ("density_activation", i32), ("random_bg_color", i32), ("linear_colors", i32),
-                ("snap_to_pixel_centers", i32), ("background_color", f32 * 3), ("loss_scale", f32), ("near_distance", f32), ("mean_density", f32)]
+                ("snap_to_pixel_centers", i32), ("background_color", f32 * 3), ("loss_scale", f32), ("near_distance", f32), ("mean_density", f32), ("color_space", i32), ("exposure", vp), ("exposure_gradient", vp)]
 
 
 class LossOut(C.Structure):
