@@ -183,6 +183,9 @@ int ngp_nerf_dataset_set_image(ngp_nerf_dataset_t d, uint32_t i, const void* hos
 int ngp_nerf_dataset_info(ngp_nerf_dataset_t d, int32_t* aabb_scale, float* scale, float* offset3, int32_t* from_mitsuba);
 /* view i as it will be uploaded (pixels point into the dataset's own copy; focal length valid after set_image) */
 int ngp_nerf_dataset_view(ngp_nerf_dataset_t d, uint32_t i, ngp_training_image* out);
+/* the end pose ("transform_matrix_end", NGP convention; equal to the start pose when the frame has none) and the rolling-shutter coefficients
+ * ("rolling_shutter": [A, B, C(, D)] of the scene or the frame) of frame i (nerf_loader.cu:190-202,648-649,676-680) */
+int ngp_nerf_dataset_view_motion(ngp_nerf_dataset_t d, uint32_t i, float* xform_end12, float* rolling_shutter4);
 int ngp_testbed_load_nerf_dataset(ngp_testbed_t t, void* stream, ngp_nerf_dataset_t d);
 /* nerf.training.set_image(frame_idx, img) (python_api.cu:49-67,583): replace one view's pixels (same size and type as
  * given to set_nerf_dataset) from HOST memory.  The copy is ordered after everything already queued on `stream` and before the
@@ -196,6 +199,12 @@ int ngp_testbed_set_training_image(ngp_testbed_t t, void* stream, uint32_t frame
 int ngp_testbed_set_camera_intrinsics(ngp_testbed_t t, void* stream, int32_t frame_idx, float fx, float fy, float cx, float cy,
                                       float k1, float k2, float p1, float p2);
 int ngp_testbed_set_camera_extrinsics(ngp_testbed_t t, void* stream, int32_t frame_idx, const float* camera_to_world, int32_t convert_to_ngp);
+/* nerf.training.set_camera_extrinsics_rolling_shutter(frame_idx, camera_to_world_start, camera_to_world_end, rolling_shutter, convert_to_ngp)
+ * (python_api.cu:606-617, testbed_nerf.cu:2896-2915): the pose at the start and at the end of the exposure and (A, B, C, D); every training ray
+ * of the view gets the camera interpolated at pixel time A + B u + C v + D motionblur_time (get_xform_given_rolling_shutter, common_device.cuh:401-408:
+ * position linearly, rotation by quaternion slerp).  The loader sets both from "transform_matrix_start" / "_end" and "rolling_shutter". */
+int ngp_testbed_set_camera_extrinsics_rolling_shutter(ngp_testbed_t t, void* stream, int32_t frame_idx, const float* camera_to_world_start,
+                                                      const float* camera_to_world_end, const float* rolling_shutter4, int32_t convert_to_ngp);
 /* Testbed.reset(reset_density_grid) (python_api.cu: reset_network): fresh parameters, optimizer state and counters */
 int ngp_testbed_reset(ngp_testbed_t t, int32_t reset_density_grid);
 int ngp_testbed_set_image(ngp_testbed_t t, void* stream, const float* host_rgba, int32_t width, int32_t height);   /* image mode */

@@ -100,10 +100,12 @@ SYMBOLS = {
     "ngp_nerf_dataset_set_image": (i32, [vp, u32, vp, C.c_int32, C.c_int32, C.c_int32]),
     "ngp_nerf_dataset_info": (i32, [vp, C.POINTER(C.c_int32), C.POINTER(f32), C.POINTER(f32), C.POINTER(C.c_int32)]),
     "ngp_nerf_dataset_view": (i32, [vp, u32, C.POINTER(TrainingImage)]),
+    "ngp_nerf_dataset_view_motion": (i32, [vp, u32, vp, vp]),
     "ngp_testbed_load_nerf_dataset": (i32, [vp, vp, vp]),
     "ngp_testbed_set_training_image": (i32, [vp, vp, u32, vp]),
     "ngp_testbed_set_camera_intrinsics": (i32, [vp, vp, C.c_int32, f32, f32, f32, f32, f32, f32, f32, f32]),
     "ngp_testbed_set_camera_extrinsics": (i32, [vp, vp, C.c_int32, vp, C.c_int32]),
+    "ngp_testbed_set_camera_extrinsics_rolling_shutter": (i32, [vp, vp, C.c_int32, vp, vp, vp, C.c_int32]),
     "ngp_testbed_reset": (i32, [vp, C.c_int32]),
     "ngp_testbed_set_image": (i32, [vp, vp, vp, C.c_int32, C.c_int32]),
     "ngp_testbed_override_sdf_training_data": (i32, [vp, vp, vp, vp, u32, vp, vp, f32]),

@@ -258,6 +258,11 @@ int ngp_nerf_dataset_view(ngp_nerf_dataset_t d, uint32_t i, ngp_training_image* 
     fill_view(d->ds.frames[i], out);
     NGP_API_END
 }
+int ngp_nerf_dataset_view_motion(ngp_nerf_dataset_t d, uint32_t i, float* xform_end12, float* rolling_shutter4) {
+    NGP_API_BEGIN NGP_CHECK(d && xform_end12 && rolling_shutter4, "null argument"); NGP_CHECK(i < d->ds.n_images(), "Invalid frame index");
+    memcpy(xform_end12, d->ds.frames[i].xform_end, 48); memcpy(rolling_shutter4, d->ds.frames[i].rolling_shutter, 16);
+    NGP_API_END
+}
 int ngp_testbed_load_nerf_dataset(ngp_testbed_t t, void* stream, ngp_nerf_dataset_t d) {
     NGP_API_BEGIN require_device(); NGP_CHECK(t && d, "null argument");
     NGP_CHECK(d->ds.complete(), "load_nerf_dataset: every frame needs its decoded pixels first (ngp_nerf_dataset_set_image)");
@@ -267,6 +272,12 @@ int ngp_testbed_load_nerf_dataset(ngp_testbed_t t, void* stream, ngp_nerf_datase
     t->tb.set_nerf_dataset(S(stream), (uint32_t)views.size(), reinterpret_cast<const HostImage*>(views.data()), d->ds.aabb_scale);
     t->tb.set_dataset_scale_offset(d->ds.scale, d->ds.offset);
     t->tb.apply_dataset_view_hints(d->ds.has_render_aabb, d->ds.render_aabb, d->ds.up);
+    for (size_t i = 0; i < d->ds.frames.size(); ++i) {   // end poses and rolling shutter (already in the NGP convention)
+        const ngp::DatasetFrame& f = d->ds.frames[i];
+        const bool moving = memcmp(f.xform, f.xform_end, sizeof(f.xform)) != 0;
+        const bool shutter = f.rolling_shutter[0] != 0.f || f.rolling_shutter[1] != 0.f || f.rolling_shutter[2] != 0.f || f.rolling_shutter[3] != 0.f;
+        if (moving || shutter) t->tb.set_camera_extrinsics_rolling_shutter(S(stream), (int)i, f.xform, f.xform_end, f.rolling_shutter, false);
+    }
     NGP_API_END
 }
 int ngp_testbed_set_training_image(ngp_testbed_t t, void* stream, uint32_t frame_idx, const void* pixels_host) {
@@ -278,6 +289,12 @@ int ngp_testbed_set_camera_intrinsics(ngp_testbed_t t, void* stream, int32_t fra
                                       float k1, float k2, float p1, float p2) {
     NGP_API_BEGIN require_device(); NGP_CHECK(t, "null argument");
     t->tb.set_camera_intrinsics(S(stream), frame_idx, fx, fy, cx, cy, k1, k2, p1, p2);
+    NGP_API_END
+}
+int ngp_testbed_set_camera_extrinsics_rolling_shutter(ngp_testbed_t t, void* stream, int32_t frame_idx, const float* c2w_start, const float* c2w_end,
+                                                      const float* rolling_shutter4, int32_t convert_to_ngp) {
+    NGP_API_BEGIN require_device(); NGP_CHECK(t && c2w_start && c2w_end && rolling_shutter4, "null argument");
+    t->tb.set_camera_extrinsics_rolling_shutter(S(stream), frame_idx, c2w_start, c2w_end, rolling_shutter4, convert_to_ngp != 0);
     NGP_API_END
 }
 int ngp_testbed_set_camera_extrinsics(ngp_testbed_t t, void* stream, int32_t frame_idx, const float* c2w, int32_t convert_to_ngp) {

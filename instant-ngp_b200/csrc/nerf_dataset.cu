@@ -55,7 +55,7 @@ static float num(const Json& j) {
 }
 static float fov_to_focal_length(int resolution, float degrees) { return 0.5f * (float)resolution / tanf(0.5f * degrees * 3.14159265358979323846f / 180.0f); }
 
-struct LensState { int mode = LENS_PERSPECTIVE; float params[4] = {0, 0, 0, 0}; float principal_point[2] = {0.5f, 0.5f}; };
+struct LensState { int mode = LENS_PERSPECTIVE; float params[4] = {0, 0, 0, 0}; float principal_point[2] = {0.5f, 0.5f}; float rolling_shutter[4] = {0, 0, 0, 0}; };
 
 // read_lens (nerf_loader.cu:161-227), the modes this path implements (Perspective, OpenCV)
 static void read_lens(const Json& json, LensState& l) {
@@ -67,6 +67,11 @@ static void read_lens(const Json& json, LensState& l) {
     read("k1", 0); read("k2", 1); read("k3", 2); read("k4", 3); read("p1", 2); read("p2", 3);
     if (json.contains("cx")) l.principal_point[0] = num(json.at("cx")) / num(json.at("w"));
     if (json.contains("cy")) l.principal_point[1] = num(json.at("cy")) / num(json.at("h"));
+    if (json.contains("rolling_shutter")) {   // [A, B, C(, D)]: pixel time = A + B u + C v + D motionblur_time (:190-202)
+        const Json& rs = json.at("rolling_shutter");
+        const float d = rs.arr.size() >= 4 ? num(rs.arr[3]) : 0.f;
+        l.rolling_shutter[0] = num(rs.arr.at(0)); l.rolling_shutter[1] = num(rs.arr.at(1)); l.rolling_shutter[2] = num(rs.arr.at(2)); l.rolling_shutter[3] = d;
+    }
     if (json.contains("ftheta_p0") || json.contains("latlong") || json.contains("equirectangular") || mode == -1)
         throw Error("transforms.json: only the Perspective and OpenCV lens models are implemented on this path");
     if (mode != LENS_PERSPECTIVE) l.mode = mode;
@@ -168,16 +173,18 @@ NerfDataset::NerfDataset(const std::vector<std::string>& json_paths) {
             d.file_path = fr.at("file_path").str;
             d.resolved_path = resolve_path(base, d.file_path);
             const Json& mat = fr.contains("transform_matrix_start") ? fr.at("transform_matrix_start") : fr.at("transform_matrix");
-            for (int m = 0; m < 3; ++m) for (int n = 0; n < 4; ++n) d.xform_nerf[n * 3 + m] = num(mat.arr.at(m).arr.at(n));
+            const Json& mat_end = fr.contains("transform_matrix_end") ? fr.at("transform_matrix_end") : mat;   // :648-649
+            for (int m = 0; m < 3; ++m) for (int n = 0; n < 4; ++n) { d.xform_nerf[n * 3 + m] = num(mat.arr.at(m).arr.at(n)); d.xform_end_nerf[n * 3 + m] = num(mat_end.arr.at(m).arr.at(n)); }
             LensState l = lens;           // "set these from the base settings", then "see if there is a per-frame override"
             read_lens(fr, l);
             d.lens_mode = l.mode; memcpy(d.lens_params, l.params, sizeof(l.params)); memcpy(d.principal_point, l.principal_point, sizeof(l.principal_point));
+            memcpy(d.rolling_shutter, l.rolling_shutter, sizeof(l.rolling_shutter));
             nerf_matrix_to_ngp(d.xform_nerf, d.xform);
             frames.push_back(std::move(d));
         }
     }
     // scale / offset of a later json apply to every frame in the reference too (conversion runs after all jsons are read)
-    for (DatasetFrame& d : frames) nerf_matrix_to_ngp(d.xform_nerf, d.xform);
+    for (DatasetFrame& d : frames) { nerf_matrix_to_ngp(d.xform_nerf, d.xform); nerf_matrix_to_ngp(d.xform_end_nerf, d.xform_end); }
 }
 
 void NerfDataset::set_image(size_t i, const void* pixels, int data_type, int w, int h) {

@@ -15,6 +15,8 @@ struct DatasetFrame {
     std::string resolved_path;    // base directory applied, extension searched (nerf_loader.cu:306-317)
     float xform_nerf[12];         // transform_matrix rows 0-2 as a column-major mat4x3 (nerf_loader.cu:679-684)
     float xform[12];              // nerf_matrix_to_ngp (nerf_loader.h:120-140)
+    float xform_end_nerf[12], xform_end[12];   // transform_matrix_end (default: the start pose), same conversions
+    float rolling_shutter[4] = {0, 0, 0, 0};   // "rolling_shutter" of the scene or the frame (nerf_loader.cu:190-202)
     float focal_length[2] = {0, 0}; bool has_focal = false;
     float principal_point[2] = {0.5f, 0.5f};
     int lens_mode = 0; float lens_params[4] = {0, 0, 0, 0};

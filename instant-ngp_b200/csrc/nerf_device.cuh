@@ -35,7 +35,9 @@ struct ImageMeta {
     int res[2];
     float principal_point[2];
     float focal_length[2];
-    float xform[12];
+    float xform[12];            // TrainingXForm::start (mat4x3, column major)
+    float xform_end[12];        // TrainingXForm::end; equal to xform unless the data set gives transform_matrix_start / _end
+    float rolling_shutter[4];   // TrainingImageMetadata::rolling_shutter (nerf_loader.h:44): pixel time = A + B u + C v + D motionblur_time
 };
 
 // ---- stepping (what testbed_nerf.cu:124-184 computes; evaluated through struct Cone below) ----
@@ -269,6 +271,49 @@ NGP_HD void uv_to_ray(const float* xform, const int* res, const float* focal, co
     if (lens_mode == LENS_OPENCV) opencv_undistort(lens_params, &dir.x, &dir.y);
     d = mat3_mul(xform, dir);
     o = v3(xform[9], xform[10], xform[11]);
+}
+// get_xform_given_rolling_shutter (common_device.cuh:401-408): the camera of ONE ray — position interpolated linearly between the start and
+// end pose of the view at the ray's pixel time, rotation by quaternion slerp.  Every training ray of the reference goes through it, also when
+// start == end and the shutter is (0,0,0,0): the rotation then makes the round trip matrix -> quaternion -> normalise -> matrix, which is not
+// the identity in floating point, so the round trip is part of the ray.  GLM's evaluation order is restated operation by operation
+// (gtc/quaternion.inl:47-72,81-123 quat_cast / mat3_cast; ext/quaternion_common.inl:41-73 slerp; ext/quaternion_geometric.inl:11-24 normalize;
+// detail/type_quat.inl:17-24 dot).  q = (w, x, y, z); matrices are column major: m[c * 3 + r].
+NGP_HD void quat_cast3(const float* m, float* q) {
+    const float fx = m[0] - m[4] - m[8], fy = m[4] - m[0] - m[8], fz = m[8] - m[0] - m[4], fw = m[0] + m[4] + m[8];
+    int biggest = 0; float fb = fw;
+    if (fx > fb) { fb = fx; biggest = 1; }
+    if (fy > fb) { fb = fy; biggest = 2; }
+    if (fz > fb) { fb = fz; biggest = 3; }
+    const float bv = sqrtf(fb + 1.0f) * 0.5f, mult = 0.25f / bv;
+    // m[c][r]: m[1][2] = m[5], m[2][1] = m[7], m[2][0] = m[6], m[0][2] = m[2], m[0][1] = m[1], m[1][0] = m[3]
+    if (biggest == 0) { q[0] = bv; q[1] = (m[5] - m[7]) * mult; q[2] = (m[6] - m[2]) * mult; q[3] = (m[1] - m[3]) * mult; }
+    else if (biggest == 1) { q[0] = (m[5] - m[7]) * mult; q[1] = bv; q[2] = (m[1] + m[3]) * mult; q[3] = (m[6] + m[2]) * mult; }
+    else if (biggest == 2) { q[0] = (m[6] - m[2]) * mult; q[1] = (m[1] + m[3]) * mult; q[2] = bv; q[3] = (m[5] + m[7]) * mult; }
+    else { q[0] = (m[1] - m[3]) * mult; q[1] = (m[6] + m[2]) * mult; q[2] = (m[5] + m[7]) * mult; q[3] = bv; }
+}
+NGP_HD float quat_dot(const float* a, const float* b) { return (a[0] * b[0] + a[1] * b[1]) + (a[2] * b[2] + a[3] * b[3]); }
+NGP_HD void xform_given_rolling_shutter(const float* start, const float* end, const float* rolling_shutter, float u, float v, float motionblur_time, float* out) {
+    const float pixel_t = rolling_shutter[0] + rolling_shutter[1] * u + rolling_shutter[2] * v + rolling_shutter[3] * motionblur_time;
+    float qa[4], qb[4], z[4], q[4];
+    quat_cast3(start, qa); quat_cast3(end, qb);
+    float cos_theta = quat_dot(qa, qb);
+    for (int k = 0; k < 4; ++k) z[k] = qb[k];
+    if (cos_theta < 0.0f) { for (int k = 0; k < 4; ++k) z[k] = -qb[k]; cos_theta = -cos_theta; }
+    if (cos_theta > 1.0f - 1.1920928955078125e-7f) {        // glm::epsilon<float>(): linear interpolation, mix(x, y, a) = x (1 - a) + y a
+        for (int k = 0; k < 4; ++k) q[k] = qa[k] * (1.0f - pixel_t) + z[k] * pixel_t;
+    } else {
+        const float angle = acosf(cos_theta), s0 = sinf((1.0f - pixel_t) * angle), s1 = sinf(pixel_t * angle), sd = sinf(angle);
+        for (int k = 0; k < 4; ++k) q[k] = (s0 * qa[k] + s1 * z[k]) / sd;
+    }
+    const float len = sqrtf(quat_dot(q, q));
+    if (len <= 0.0f) { q[0] = 1.0f; q[1] = q[2] = q[3] = 0.0f; }
+    else { const float inv = 1.0f / len; for (int k = 0; k < 4; ++k) q[k] = q[k] * inv; }
+    const float w = q[0], x = q[1], y = q[2], zz = q[3];
+    const float qxx = x * x, qyy = y * y, qzz = zz * zz, qxz = x * zz, qxy = x * y, qyz = y * zz, qwx = w * x, qwy = w * y, qwz = w * zz;
+    out[0] = 1.0f - 2.0f * (qyy + qzz); out[1] = 2.0f * (qxy + qwz); out[2] = 2.0f * (qxz - qwy);
+    out[3] = 2.0f * (qxy - qwz); out[4] = 1.0f - 2.0f * (qxx + qzz); out[5] = 2.0f * (qyz + qwx);
+    out[6] = 2.0f * (qxz + qwy); out[7] = 2.0f * (qyz - qwx); out[8] = 1.0f - 2.0f * (qxx + qyy);
+    for (int k = 0; k < 3; ++k) out[9 + k] = start[9 + k] + (end[9 + k] - start[9 + k]) * pixel_t;
 }
 NGP_HD void pos_to_uv(const ImageMeta& im, V3 pos, float* uv) {
     const float* m = im.xform;

@@ -455,9 +455,10 @@ __global__ void __launch_bounds__(SCAN_BLOCK) sampler_count_kernel(uint32_t n_ra
         float uv[2]; random_image_pos_training(rng, m.res, snap, uv);
         float texel[4]; read_rgba(m, uv[0], uv[1], texel);
         if (texel[0] >= 0.0f) {   // negative = masked-away pixel (:1430-1435)
-            (void)rng.next_float();   // motionblur_time (:1440)
-            V3 o, du; uv_to_ray(m.xform, m.res, m.focal_length, m.principal_point, m.lens_mode, m.lens_params, uv[0], uv[1], o, du);
-            if (du.x == 0.f && du.y == 0.f && du.z == 0.f) { o = v3(m.xform[9], m.xform[10], m.xform[11]); du = v3(m.xform[6], m.xform[7], m.xform[8]); }
+            const float motionblur_time = rng.next_float();   // :1440
+            float xf[12]; xform_given_rolling_shutter(m.xform, m.xform_end, m.rolling_shutter, uv[0], uv[1], motionblur_time, xf);   // :1447-1451
+            V3 o, du; uv_to_ray(xf, m.res, m.focal_length, m.principal_point, m.lens_mode, m.lens_params, uv[0], uv[1], o, du);
+            if (du.x == 0.f && du.y == 0.f && du.z == 0.f) { o = v3(xf[9], xf[10], xf[11]); du = v3(xf[6], xf[7], xf[8]); }
             const V3 d = normalize3(du);
             float tmin, tmax; aabb_ray_intersect(aabb, o, d, tmin, tmax);
             const Cone cone(cone_angle_constant);   // calc_cone_angle (:114-122)
@@ -535,6 +536,29 @@ NGP_D float div_by_stepsize_in_range(float t) {
     constexpr float S = SQRT3 / (float)NERF_STEPS, RS = 1.0f / S;
     const float q = t * RS; return fmaf(fmaf(-q, S, t), RS, q);
 }
+// General path, skip candidates: the cell a skip leaves is found from mip_from_dt(dt, pos), and dt = expf((logf(t) / L + 1) L) - t puts a whole
+// logf -> expf pair in front of the skip's own logf -> expf on the serial chain.  But the mip depends on dt only through the binary exponent of
+// 256 dt, and in the logarithmic regime dt = t * cone_angle up to the rounding of that evaluation: |x| <= 6.1 and n <= 1563 bound the error of the
+// exponent argument by 1.3e-6, i.e. dt by 3.4e-4 relative.  So with a 1e-3 margin either side the exponent is decided by t * cone_angle alone unless
+// 256 dt lies within 0.1 % of a power of two (or t within 1 % of a regime boundary) — then, and only then, the exact dt is computed.  Same mip, hence
+// the same skip, bit for bit (test_sampler_with_cascades_and_cone_angle); the A/B build (make ab, NGP_AB_OLD_MATH) keeps the exact evaluation.
+NGP_D bool mip_without_dt(float t, V3 pos, const Cone& c, uint32_t max_mip, uint32_t& mip) {
+#ifdef NGP_AB_OLD_MATH
+    return false;
+#endif
+    if (!(t > c.at * 1.01f && t < c.bt * 0.99f)) return false;
+    const float d = t * c.angle * (float)(2 * NERF_GRIDSIZE);
+    const float lo = d * 0.999f, hi = d * 1.001f;
+    mip = mip_from_pos(pos, max_mip);
+    if (hi < 1.0f) return true;            // dt * 256 < 1: mip_from_pos decides (:626-628)
+    if (lo < 1.0f) return false;
+    const int e = frexp_exponent(lo);
+    if (e != frexp_exponent(hi)) return false;
+    int v = (int)mip; const int top = (int)max_mip;
+    v = v < e ? e : (top < v ? top : v);   // tcnn::clamp(mip, e, max_cascade) (:632)
+    mip = (uint32_t)v;
+    return true;
+}
 template <bool FLAT, bool STEP, bool FAST>
 NGP_D float chain_next(float t, const RayConst& rc, const Cone& cone, uint32_t max_mip) {
     if (FLAT && FAST) {
@@ -552,6 +576,7 @@ NGP_D float chain_next(float t, const RayConst& rc, const Cone& cone, uint32_t m
     if (FLAT && STEP) { const float n = div_by_stepsize(t); return t + ((n + 1.0f) * MIN_CONE_STEPSIZE() - t); }
     const V3 pos = ray_at(rc.o, rc.d, t);
     float dt, n; uint32_t mip;
+    if (!FLAT && !STEP && mip_without_dt(t, pos, cone, max_mip, mip)) return advance_to_next_voxel(t, cone, pos, rc.d, rc.idir, mip);
     candidate_dt_mip<FLAT>(t, pos, cone, max_mip, dt, mip, n);
     return STEP ? t + dt : candidate_skip<FLAT>(t, n, pos, rc, cone, mip);
 }
@@ -676,9 +701,10 @@ __global__ void __launch_bounds__(128) sampler_classify_kernel(uint32_t n_rays, 
         float uv[2]; random_image_pos_training(rng, m.res, snap, uv);
         float texel[4]; read_rgba(m, uv[0], uv[1], texel);
         if (texel[0] >= 0.0f) {   // negative = masked-away pixel (:1430-1435)
-            (void)rng.next_float();   // motionblur_time (:1440)
-            V3 o, du; uv_to_ray(m.xform, m.res, m.focal_length, m.principal_point, m.lens_mode, m.lens_params, uv[0], uv[1], o, du);
-            if (du.x == 0.f && du.y == 0.f && du.z == 0.f) { o = v3(m.xform[9], m.xform[10], m.xform[11]); du = v3(m.xform[6], m.xform[7], m.xform[8]); }
+            const float motionblur_time = rng.next_float();   // :1440
+            float xf[12]; xform_given_rolling_shutter(m.xform, m.xform_end, m.rolling_shutter, uv[0], uv[1], motionblur_time, xf);   // :1447-1451
+            V3 o, du; uv_to_ray(xf, m.res, m.focal_length, m.principal_point, m.lens_mode, m.lens_params, uv[0], uv[1], o, du);
+            if (du.x == 0.f && du.y == 0.f && du.z == 0.f) { o = v3(xf[9], xf[10], xf[11]); du = v3(xf[6], xf[7], xf[8]); }
             const V3 d = normalize3(du);
             float tmin, tmax; aabb_ray_intersect(aabb, o, d, tmin, tmax);
             const Cone cone(cone_angle_constant);   // calc_cone_angle (:114-122)

@@ -81,12 +81,11 @@ static Json dataset_json(const std::vector<ImageMeta>& metas, const Aabb& render
         e["focal_length"] = vec_json(m.focal_length, 2);
         e["lens"] = lens_json(m);
         e["principal_point"] = vec_json(m.principal_point, 2);
-        const float rs[4] = {0.f, 0.f, 0.f, 0.f};
-        e["rolling_shutter"] = vec_json(rs, 4);
+        e["rolling_shutter"] = vec_json(m.rolling_shutter, 4);
         Json res; res.type = Json::Array; res.arr.push_back(Json::integer(m.res[0])); res.arr.push_back(Json::integer(m.res[1]));
         e["resolution"] = res;
         md.arr.push_back(e);
-        Json x; x["start"] = mat4x3_json(m.xform); x["end"] = mat4x3_json(m.xform);
+        Json x; x["start"] = mat4x3_json(m.xform); x["end"] = mat4x3_json(m.xform_end);
         xf.arr.push_back(x);
     }
     j["paths"] = paths; j["metadata"] = md; j["xforms"] = xf;
@@ -252,6 +251,8 @@ void Testbed::load_snapshot(cudaStream_t s, const std::string& path) {
                     for (int k = 0; k < 4; ++k) m.lens_params[k] = (float)md.at("lens").value(keys[k], 0.0);
                 }
                 mat4x3_from_json(d.at("xforms").arr.at(i).at("start"), m.xform);
+                if (d.at("xforms").arr.at(i).contains("end")) mat4x3_from_json(d.at("xforms").arr.at(i).at("end"), m.xform_end); else memcpy(m.xform_end, m.xform, sizeof(m.xform));
+                if (md.contains("rolling_shutter") && md.at("rolling_shutter").arr.size() == 4) for (int k = 0; k < 4; ++k) m.rolling_shutter[k] = (float)md.at("rolling_shutter").arr[k].num;
             }
             aabb_scale = (int)d.value("aabb_scale", (double)aabb_scale);
             m_ds_scale = (float)d.value("scale", (double)m_ds_scale);

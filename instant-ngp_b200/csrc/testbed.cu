@@ -118,7 +118,7 @@ void Testbed::set_nerf_dataset(cudaStream_t s, uint32_t n_images, const HostImag
         m.pixels = d; m.data_type = h.data_type; m.lens_mode = h.lens_mode;
         memcpy(m.lens_params, h.lens_params, sizeof(m.lens_params)); memcpy(m.res, h.res, sizeof(m.res));
         memcpy(m.principal_point, h.principal_point, sizeof(m.principal_point)); memcpy(m.focal_length, h.focal_length, sizeof(m.focal_length));
-        memcpy(m.xform, h.xform, sizeof(m.xform));
+        memcpy(m.xform, h.xform, sizeof(m.xform)); memcpy(m.xform_end, h.xform, sizeof(m.xform_end));   // start == end, shutter (0,0,0,0)
     }
     ImageMeta* md = m_metas.get<ImageMeta>(n_images);
     NGP_CUDA_CHECK(cudaMemcpyAsync(md, metas.data(), n_images * sizeof(ImageMeta), cudaMemcpyHostToDevice, s));
@@ -179,17 +179,30 @@ void Testbed::set_camera_intrinsics(cudaStream_t s, int frame_idx, float fx, flo
     upload_view_metadata(s, (uint32_t)frame_idx);
 }
 
-void Testbed::set_camera_extrinsics(cudaStream_t s, int frame_idx, const float* c2w, bool convert_to_ngp) {
-    NGP_CHECK(m_mode == MODE_TB_NERF && c2w, "set_camera_extrinsics: testbed is not in Nerf mode / null matrix");
-    if (frame_idx < 0 || frame_idx >= (int)m_n_images) return;   // testbed_nerf.cu:2897-2899
-    float m[12]; memcpy(m, c2w, sizeof(m));
-    if (convert_to_ngp) {   // nerf_matrix_to_ngp (nerf_loader.h:120-140)
-        for (int r = 0; r < 3; ++r) { m[3 + r] *= -1.f; m[6 + r] *= -1.f; m[9 + r] = m[9 + r] * m_ds_scale + m_ds_offset[r]; }
-        float t[12]; memcpy(t, m, sizeof(t));
-        for (int c = 0; c < 4; ++c) { m[c * 3 + 0] = t[c * 3 + 1]; m[c * 3 + 1] = t[c * 3 + 2]; m[c * 3 + 2] = t[c * 3 + 0]; }
+// set_camera_extrinsics_rolling_shutter (testbed_nerf.cu:2896-2915): start and end pose of one view + its rolling-shutter coefficients
+void Testbed::set_camera_extrinsics_rolling_shutter(cudaStream_t s, int frame_idx, const float* c2w_start, const float* c2w_end, const float* rolling_shutter4,
+                                                    bool convert_to_ngp) {
+    NGP_CHECK(m_mode == MODE_TB_NERF && c2w_start && c2w_end && rolling_shutter4, "set_camera_extrinsics_rolling_shutter: testbed is not in Nerf mode / null argument");
+    if (frame_idx < 0 || frame_idx >= (int)m_n_images) return;   // :2897-2899
+    const float* src[2] = {c2w_start, c2w_end};
+    float* dst[2] = {m_host_metas[frame_idx].xform, m_host_metas[frame_idx].xform_end};
+    for (int k = 0; k < 2; ++k) {
+        float m[12]; memcpy(m, src[k], sizeof(m));
+        if (convert_to_ngp) {   // nerf_matrix_to_ngp (nerf_loader.h:120-140)
+            for (int r = 0; r < 3; ++r) { m[3 + r] *= -1.f; m[6 + r] *= -1.f; m[9 + r] = m[9 + r] * m_ds_scale + m_ds_offset[r]; }
+            float t[12]; memcpy(t, m, sizeof(t));
+            for (int c = 0; c < 4; ++c) { m[c * 3 + 0] = t[c * 3 + 1]; m[c * 3 + 1] = t[c * 3 + 2]; m[c * 3 + 2] = t[c * 3 + 0]; }
+        }
+        memcpy(dst[k], m, sizeof(m));
     }
-    memcpy(m_host_metas[frame_idx].xform, m, sizeof(m));
+    memcpy(m_host_metas[frame_idx].rolling_shutter, rolling_shutter4, 16);
     upload_view_metadata(s, (uint32_t)frame_idx);
+}
+
+void Testbed::set_camera_extrinsics(cudaStream_t s, int frame_idx, const float* c2w, bool convert_to_ngp) {   // :2917-2919
+    const float zero[4] = {0.f, 0.f, 0.f, 0.f};
+    NGP_CHECK(m_mode == MODE_TB_NERF && c2w, "set_camera_extrinsics: testbed is not in Nerf mode / null matrix");
+    set_camera_extrinsics_rolling_shutter(s, frame_idx, c2w, c2w, zero, convert_to_ngp);
 }
 
 void Testbed::set_training_image(cudaStream_t s, uint32_t frame_idx, const void* pixels_host) {
@@ -851,7 +864,7 @@ void Testbed::set_camera_to_training_view(int v) {
     NGP_CHECK(m_mode == MODE_TB_NERF && v >= 0 && v < (int)m_n_images, "set_camera_to_training_view: no such training view");
     const ImageMeta& m = m_host_metas[v];
     float old_look_at[3]; for (int k = 0; k < 3; ++k) old_look_at[k] = camera[9 + k] + camera[6 + k] * scale;
-    memcpy(camera, m.xform, sizeof(camera));
+    xform_given_rolling_shutter(m.xform, m.xform_end, m.rolling_shutter, 0.5f, 0.5f, 0.0f, camera);   // get_xform_given_rolling_shutter(.., {0.5, 0.5}, 0) (testbed.cu:843)
     for (int k = 0; k < 2; ++k) relative_focal_length[k] = m.focal_length[k] / (float)m.res[fov_axis];
     float d = 0.f; for (int k = 0; k < 3; ++k) d += (old_look_at[k] - camera[9 + k]) * camera[6 + k];
     scale = std::max(d, 0.1f);

@@ -44,6 +44,9 @@ public:
     // scale / offset the data set was loaded with (0.33 / 0.5 for views handed over in memory)
     void set_camera_intrinsics(cudaStream_t s, int frame_idx, float fx, float fy, float cx, float cy, float k1, float k2, float p1, float p2);
     void set_camera_extrinsics(cudaStream_t s, int frame_idx, const float* camera_to_world, bool convert_to_ngp);
+    // nerf.training.set_camera_extrinsics_rolling_shutter (python_api.cu:606-617, testbed_nerf.cu:2896-2915): the pose at the start and at the end of the
+    // exposure + (A, B, C, D): a ray's camera is interpolated at pixel time A + B u + C v + D motionblur_time (common_device.cuh:401-408)
+    void set_camera_extrinsics_rolling_shutter(cudaStream_t s, int frame_idx, const float* c2w_start, const float* c2w_end, const float* rolling_shutter4, bool convert_to_ngp);
     void set_dataset_scale_offset(float scale, const float* offset3) { m_ds_scale = scale; for (int k = 0; k < 3; ++k) m_ds_offset[k] = offset3[k]; }
     // Testbed::reset_network(clear_density_grid) (python_api.cu "reset"): fresh parameters, optimizer state, counters
     void reset(bool reset_density_grid);

@@ -257,7 +257,8 @@ class Testbed:
                                      "optimize_exposure": "optimize_exposure", "exposure_l2_reg": "exposure_l2_reg",
                                      "n_steps_between_cam_updates": "n_steps_between_cam_updates"},
                               {"set_image": self.set_training_image, "set_camera_intrinsics": self.set_camera_intrinsics,
-                               "set_camera_extrinsics": self.set_camera_extrinsics, "dataset": _Dataset(self),
+                               "set_camera_extrinsics": self.set_camera_extrinsics,
+                               "set_camera_extrinsics_rolling_shutter": self.set_camera_extrinsics_rolling_shutter, "dataset": _Dataset(self),
                                "n_images_for_training": _Lazy(self.n_training_views)})
         object.__setattr__(self, "nerf", _Namespace(self, {"rgb_activation": "rgb_activation", "density_activation": "density_activation",
                                                            "cone_angle_constant": "cone_angle_constant",
@@ -429,6 +430,11 @@ class Testbed:
             arr[i].xform = (C.c_float * 12)(*[float(x) for x in np.asarray(v["xform"], np.float32).reshape(-1)])
         check(lib().ngp_testbed_set_nerf_dataset(self._h, _stream(), len(views), arr, int(aabb_scale)))
         self._keep.clear()
+        for i, v in enumerate(views):      # optional: "xform_end" (NGP convention, like "xform") and "rolling_shutter" (A, B, C, D)
+            if v.get("xform_end") is not None or any(float(x) != 0.0 for x in v.get("rolling_shutter", (0, 0, 0, 0))):
+                to34 = lambda m: np.asarray(m, np.float32).reshape(4, 3).T
+                self.set_camera_extrinsics_rolling_shutter(i, to34(v["xform"]), to34(v["xform"] if v.get("xform_end") is None else v["xform_end"]),
+                                                           v.get("rolling_shutter", (0, 0, 0, 0)), convert_to_ngp=False)
 
     def load_training_data(self, path):
         """Testbed.load_training_data(path) (python_api.cu:398) for a NeRF scene: `path` is a transforms.json, a directory holding
@@ -488,6 +494,20 @@ class Testbed:
             raise RuntimeError("camera_to_world must be a 3x4 or 4x4 matrix")
         col_major = np.ascontiguousarray(m[:3, :4].T).reshape(-1)
         check(lib().ngp_testbed_set_camera_extrinsics(self._h, _stream(), int(frame_idx), col_major.ctypes.data_as(C.c_void_p), int(convert_to_ngp)))
+
+    def set_camera_extrinsics_rolling_shutter(self, frame_idx, camera_to_world_start, camera_to_world_end, rolling_shutter, convert_to_ngp=True):
+        """nerf.training.set_camera_extrinsics_rolling_shutter (python_api.cu:606-617): 3x4 (rows) or 4x4 matrices, rolling_shutter = (A, B, C, D)"""
+        mats = []
+        for m in (camera_to_world_start, camera_to_world_end):
+            m = np.asarray(m, np.float32)
+            if m.shape not in ((3, 4), (4, 4)):
+                raise RuntimeError("camera_to_world must be a 3x4 or 4x4 matrix")
+            mats.append(np.ascontiguousarray(m[:3, :4].T).reshape(-1))
+        rs = np.ascontiguousarray(np.asarray(rolling_shutter, np.float32).reshape(-1))
+        if rs.size != 4:
+            raise RuntimeError("rolling_shutter must have 4 components")
+        check(lib().ngp_testbed_set_camera_extrinsics_rolling_shutter(self._h, _stream(), int(frame_idx), mats[0].ctypes.data_as(C.c_void_p),
+                                                                      mats[1].ctypes.data_as(C.c_void_p), rs.ctypes.data_as(C.c_void_p), int(convert_to_ngp)))
 
     def reset(self, reset_density_grid=True):
         check(lib().ngp_testbed_reset(self._h, int(reset_density_grid)))

@@ -63,6 +63,9 @@ def read_lens(j, lens):
         lens["pp"][0] = F(j["cx"]) / F(j["w"])
     if "cy" in j:
         lens["pp"][1] = F(j["cy"]) / F(j["h"])
+    if "rolling_shutter" in j:      # nerf_loader.cu:190-202: [A, B, C] or [A, B, C, D]
+        rs = j["rolling_shutter"]
+        lens["rolling_shutter"] = [F(rs[0]), F(rs[1]), F(rs[2]), F(rs[3]) if len(rs) >= 4 else F(0)]
     if mode:
         lens["mode"] = mode
 
@@ -108,7 +111,7 @@ def load(json_path, resolutions=None):
         scale = F(0.66); offset = np.full(3, F(0.25) * scale, F)
     if "scale" in j:
         scale = F(j["scale"])
-    lens = {"mode": 0, "params": [F(0)] * 4, "pp": [F(0.5), F(0.5)]}
+    lens = {"mode": 0, "params": [F(0)] * 4, "pp": [F(0.5), F(0.5)], "rolling_shutter": [F(0)] * 4}
     read_lens(j, lens)
     aabb_scale = int(j.get("aabb_scale", 1))
     if "offset" in j:
@@ -121,11 +124,12 @@ def load(json_path, resolutions=None):
         offset = ((hi + lo) * F(0.5)) * -scale + F(0.5)
     out = []
     for i, f in enumerate(frames):
-        l = {"mode": lens["mode"], "params": list(lens["params"]), "pp": list(lens["pp"])}
+        l = {"mode": lens["mode"], "params": list(lens["params"]), "pp": list(lens["pp"]), "rolling_shutter": list(lens["rolling_shutter"])}
         read_lens(f, l)
         m = f.get("transform_matrix_start", f.get("transform_matrix"))
+        m_end = f.get("transform_matrix_end", m)             # nerf_loader.cu:648-649
         rec = dict(path=resolve_path(base, f["file_path"]), xform=nerf_matrix_to_ngp(m, scale, offset, from_mitsuba), pp=l["pp"], lens_mode=l["mode"],
-                   lens_params=l["params"], focal=None)
+                   lens_params=l["params"], focal=None, xform_end=nerf_matrix_to_ngp(m_end, scale, offset, from_mitsuba), rolling_shutter=l["rolling_shutter"])
         if resolutions is not None:
             res = resolutions[i]
             fl = read_focal_length(j, res)

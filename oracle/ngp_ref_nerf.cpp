@@ -7,6 +7,7 @@
 #include "ngp_ref_nerf.h"
 #include "../include/ngp_b200_math.h"
 #include <cmath>
+#include <cfloat>
 #include <cstring>
 #include <vector>
 #include <algorithm>
@@ -102,6 +103,49 @@ static inline void ld_random_pixel_offset(uint32_t spp, float* off) {   // rando
 
 // ---- colour (common_device.cuh:75-121) ----
 extern "C" float ref_srgb_to_linear(float s) { return s <= 0.04045f ? s / 12.92f : powf((s + 0.055f) / 1.055f, 2.4f); }
+// ---- rolling shutter: one camera per ray ----
+// glm::quat_cast(mat3) -> (w, x, y, z); m is column major, m[c][r] = a[c * 3 + r]
+static void quat_from_mat3(const float* a, float* q) {
+    float four_x = a[0] - a[4] - a[8], four_y = a[4] - a[0] - a[8], four_z = a[8] - a[0] - a[4], four_w = a[0] + a[4] + a[8];
+    int which = 0; float big = four_w;
+    if (four_x > big) { big = four_x; which = 1; }
+    if (four_y > big) { big = four_y; which = 2; }
+    if (four_z > big) { big = four_z; which = 3; }
+    float val = sqrtf(big + 1.0f) * 0.5f, mult = 0.25f / val;
+    float m12 = a[1 * 3 + 2], m21 = a[2 * 3 + 1], m20 = a[2 * 3 + 0], m02 = a[0 * 3 + 2], m01 = a[0 * 3 + 1], m10 = a[1 * 3 + 0];
+    switch (which) {
+        case 0: q[0] = val; q[1] = (m12 - m21) * mult; q[2] = (m20 - m02) * mult; q[3] = (m01 - m10) * mult; break;
+        case 1: q[0] = (m12 - m21) * mult; q[1] = val; q[2] = (m01 + m10) * mult; q[3] = (m20 + m02) * mult; break;
+        case 2: q[0] = (m20 - m02) * mult; q[1] = (m01 + m10) * mult; q[2] = val; q[3] = (m12 + m21) * mult; break;
+        default: q[0] = (m01 - m10) * mult; q[1] = (m20 + m02) * mult; q[2] = (m12 + m21) * mult; q[3] = val; break;
+    }
+}
+static float qdot(const float* a, const float* b) { float t0 = a[0] * b[0], t1 = a[1] * b[1], t2 = a[2] * b[2], t3 = a[3] * b[3]; return (t0 + t1) + (t2 + t3); }
+extern "C" void ref_xform_given_rolling_shutter(const float* start, const float* end, const float* rs, float u, float v, float motionblur_time, float* out) {
+    float pixel_t = rs[0] + rs[1] * u + rs[2] * v + rs[3] * motionblur_time;
+    float x[4], y[4], z[4], r[4];
+    quat_from_mat3(start, x); quat_from_mat3(end, y);
+    memcpy(z, y, sizeof(z));
+    float cos_theta = qdot(x, y);
+    if (cos_theta < 0.0f) { for (int k = 0; k < 4; ++k) z[k] = -y[k]; cos_theta = -cos_theta; }
+    if (cos_theta > 1.0f - FLT_EPSILON) {
+        for (int k = 0; k < 4; ++k) r[k] = x[k] * (1.0f - pixel_t) + z[k] * pixel_t;       // glm::mix
+    } else {
+        float angle = acosf(cos_theta);
+        float sa = sinf((1.0f - pixel_t) * angle), sb = sinf(pixel_t * angle), sd = sinf(angle);
+        for (int k = 0; k < 4; ++k) r[k] = (sa * x[k] + sb * z[k]) / sd;
+    }
+    float len = sqrtf(qdot(r, r));
+    if (len <= 0.0f) { r[0] = 1.0f; r[1] = r[2] = r[3] = 0.0f; }
+    else { float one_over = 1.0f / len; for (int k = 0; k < 4; ++k) r[k] = r[k] * one_over; }
+    float qw = r[0], qx = r[1], qy = r[2], qz = r[3];
+    float qxx = qx * qx, qyy = qy * qy, qzz = qz * qz, qxz = qx * qz, qxy = qx * qy, qyz = qy * qz, qwx = qw * qx, qwy = qw * qy, qwz = qw * qz;
+    out[0] = 1.0f - 2.0f * (qyy + qzz); out[1] = 2.0f * (qxy + qwz); out[2] = 2.0f * (qxz - qwy);
+    out[3] = 2.0f * (qxy - qwz); out[4] = 1.0f - 2.0f * (qxx + qzz); out[5] = 2.0f * (qyz + qwx);
+    out[6] = 2.0f * (qxz + qwy); out[7] = 2.0f * (qyz - qwx); out[8] = 1.0f - 2.0f * (qxx + qyy);
+    for (int k = 0; k < 3; ++k) out[9 + k] = start[9 + k] + (end[9 + k] - start[9 + k]) * pixel_t;
+}
+
 static float srgb_to_linear_derivative(float s) { return s <= 0.04045f ? 1.0f / 12.92f : 2.4f / 1.055f * powf((s + 0.055f) / 1.055f, 1.4f); }   // common_device.cuh:87-93
 extern "C" float ref_linear_to_srgb(float l) { return l < 0.0031308f ? 12.92f * l : 1.055f * powf(l, 0.41666f) - 0.055f; }
 
@@ -444,10 +488,12 @@ extern "C" void ref_generate_training_samples(uint32_t n_rays, const RefAabb* aa
         float uv[2]; random_image_pos_training(&rng, m->res, snap, uv);
         float texel[4]; read_rgba(m, uv, texel);
         if (texel[0] < 0.0f) continue;                      // masked-away pixel (:1430-1435)
-        (void)ref_pcg32_next_float(&rng);                   // motionblur_time (:1440); max_level not drawn (rand training off)
-        float ro[3], rd[3]; ref_uv_to_ray(m, uv, ro, rd);
+        const float motionblur_time = ref_pcg32_next_float(&rng);   // :1440; max_level not drawn (rand training off)
+        RefImage at_t = *m;                                 // the view with the camera of THIS ray (:1447-1451)
+        ref_xform_given_rolling_shutter(m->xform, m->xform_end, m->rolling_shutter, uv[0], uv[1], motionblur_time, at_t.xform);
+        float ro[3], rd[3]; ref_uv_to_ray(&at_t, uv, ro, rd);
         V3 o = ld3(ro), du = ld3(rd);
-        if (du.x == 0.f && du.y == 0.f && du.z == 0.f) { o = v3(m->xform[9], m->xform[10], m->xform[11]); du = v3(m->xform[6], m->xform[7], m->xform[8]); }
+        if (du.x == 0.f && du.y == 0.f && du.z == 0.f) { o = v3(at_t.xform[9], at_t.xform[10], at_t.xform[11]); du = v3(at_t.xform[6], at_t.xform[7], at_t.xform[8]); }
         V3 d = normalize3(du);
         float tmm[2]; float oo[3] = {o.x, o.y, o.z}, dd[3] = {d.x, d.y, d.z};
         ref_aabb_ray_intersect(aabb, oo, dd, tmm);

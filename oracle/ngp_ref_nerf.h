@@ -32,8 +32,13 @@ typedef struct RefImage {
     int32_t res[2];
     float principal_point[2];
     float focal_length[2];
-    float xform[12];           // mat4x3 column-major: x-axis, y-axis, z-axis, position
+    float xform[12];           // mat4x3 column-major: x-axis, y-axis, z-axis, position (TrainingXForm::start)
+    float xform_end[12];       // TrainingXForm::end (== xform unless the data set has transform_matrix_end)
+    float rolling_shutter[4];  // TrainingImageMetadata::rolling_shutter (nerf_loader.h:44)
 } RefImage;
+// get_xform_given_rolling_shutter (common_device.cuh:401-408) with GLM's quat_cast / slerp / normalize / mat3_cast restated
+// (dependencies/glm/glm/gtc/quaternion.inl:47-72,81-123; ext/quaternion_common.inl:41-73; ext/quaternion_geometric.inl:11-24)
+void ref_xform_given_rolling_shutter(const float* start, const float* end, const float* rolling_shutter, float u, float v, float motionblur_time, float* out12);
 
 typedef struct RefAabb { float min[3]; float max[3]; } RefAabb;
 

@@ -30,7 +30,7 @@ class AdamCfg(C.Structure):
 
 class Image(C.Structure):
     _fields_ = [("pixels", vp), ("data_type", C.c_int32), ("lens_mode", C.c_int32), ("lens_params", f32 * 4), ("res", C.c_int32 * 2),
-                ("principal_point", f32 * 2), ("focal_length", f32 * 2), ("xform", f32 * 12)]
+                ("principal_point", f32 * 2), ("focal_length", f32 * 2), ("xform", f32 * 12), ("xform_end", f32 * 12), ("rolling_shutter", f32 * 4)]
 
 
 class Aabb(C.Structure):
@@ -210,13 +210,15 @@ def adam_step(cfg, master, params_h, grads_h, m, v, steps):
     lib().ref_adam_step(C.byref(cfg), u64(master.size), P(master), P(params_h), P(grads_h), P(m), P(v), P(steps))
 
 
-def make_image(pixels, data_type, res, focal, xform, principal=(0.5, 0.5), lens_mode=0, lens_params=(0, 0, 0, 0)):
+def make_image(pixels, data_type, res, focal, xform, principal=(0.5, 0.5), lens_mode=0, lens_params=(0, 0, 0, 0), xform_end=None, rolling_shutter=(0, 0, 0, 0)):
     im = Image()
     im.pixels = pixels.ctypes.data
     im.data_type = data_type; im.lens_mode = lens_mode
     im.lens_params = (f32 * 4)(*lens_params); im.res = (C.c_int32 * 2)(*res)
     im.principal_point = (f32 * 2)(*principal); im.focal_length = (f32 * 2)(*focal)
     im.xform = (f32 * 12)(*[float(v) for v in np.asarray(xform, np.float32).reshape(-1)])
+    im.xform_end = (f32 * 12)(*[float(v) for v in np.asarray(xform if xform_end is None else xform_end, np.float32).reshape(-1)])
+    im.rolling_shutter = (f32 * 4)(*[float(v) for v in rolling_shutter])
     return im
 
 
@@ -237,7 +239,7 @@ def images_from_views(views):
         keep.append(px)
         h, w = px.shape[:2]
         arr[i] = make_image(px, 0 if px.dtype == np.uint8 else 1, (w, h), v["focal_length"], v["xform"], v.get("principal_point", (0.5, 0.5)),
-                            int(v.get("lens_mode", 0)), v.get("lens_params", (0, 0, 0, 0)))
+                            int(v.get("lens_mode", 0)), v.get("lens_params", (0, 0, 0, 0)), v.get("xform_end"), v.get("rolling_shutter", (0, 0, 0, 0)))
     return arr, keep
 
 
@@ -276,6 +278,16 @@ def compute_loss(n_rays, aabb, seed, skip, max_compacted, rays_counter, cfg, ima
     lib().ref_compute_loss(u32(n_rays), C.byref(aabb), u32(0), u64(seed), u64(skip), u32(max_compacted), u32(rays_counter), C.byref(cfg),
                            u32(len(images)), images, P(net_out_h), P(ray_indices), P(rays), P(coords), C.byref(out))
     return dict(dloss=dloss, coords_compacted=cc, loss=loss, numsteps=ns, rgb_ray=rgb_ray, compacted_counter=out.compacted_counter)
+
+
+def xform_given_rolling_shutter(start, end=None, rolling_shutter=(0, 0, 0, 0), u=0.5, v=0.5, motionblur_time=0.0):
+    """get_xform_given_rolling_shutter (common_device.cuh:401-408) -> 12 floats, column major"""
+    a = np.ascontiguousarray(np.asarray(start, np.float32).reshape(-1)); b = a if end is None else np.ascontiguousarray(np.asarray(end, np.float32).reshape(-1))
+    rs = np.ascontiguousarray(np.asarray(rolling_shutter, np.float32)); out = np.zeros(12, np.float32)
+    fn = lib().ref_xform_given_rolling_shutter
+    fn.argtypes = [vp, vp, vp, f32, f32, f32, vp]; fn.restype = None
+    fn(P(a), P(b), P(rs), float(u), float(v), float(motionblur_time), P(out))
+    return out
 
 
 def render_nerf(rcfg, net_cfg, params_h, bitfield):

@@ -23,6 +23,13 @@ using namespace ngp;
 static BoundingBox make_bb(const float* mn, const float* mx) { return BoundingBox(vec3(mn[0], mn[1], mn[2]), vec3(mx[0], mx[1], mx[2])); }
 
 extern "C" {
+// get_xform_given_rolling_shutter (common_device.cuh:401-408) through the mount's own GLM; matrices column major [12]
+void shim_get_xform_given_rolling_shutter(const float* start, const float* end, const float* rs, float u, float v, float motionblur_time, float* out) {
+    TrainingXForm x;
+    for (int c = 0; c < 4; ++c) for (int r = 0; r < 3; ++r) { x.start[c][r] = start[c * 3 + r]; x.end[c][r] = end[c * 3 + r]; }
+    mat4x3 m = get_xform_given_rolling_shutter(x, vec4(rs[0], rs[1], rs[2], rs[3]), vec2(u, v), motionblur_time);
+    for (int c = 0; c < 4; ++c) for (int r = 0; r < 3; ++r) out[c * 3 + r] = m[c][r];
+}
 float shim_ld_random_val(uint32_t index, uint32_t seed) { return ld_random_val(index, seed); }
 void shim_ld_random_val_2d(uint32_t index, uint32_t seed, float* out) { vec2 v = ld_random_val_2d(index, seed); out[0] = v.x; out[1] = v.y; }
 float shim_srgb_to_linear(float x) { return srgb_to_linear(x); }

@@ -228,6 +228,61 @@ def test_walk_ahead_is_adopted_and_bit_exact(env, ref, n_warm):
     assert runs[0] == runs[1]
 
 
+def _perturbed_pose(xform, rng, angle, shift):
+    """a pose `angle` radians and `shift` units away from xform (12 floats, column major)"""
+    m = np.asarray(xform, np.float64).reshape(4, 3).T                       # 3 x 4
+    w = rng.normal(size=3); w *= angle / np.linalg.norm(w)
+    k = np.array([[0, -w[2], w[1]], [w[2], 0, -w[0]], [-w[1], w[0], 0]])
+    r = np.eye(3) + np.sin(angle) / angle * k + (1 - np.cos(angle)) / angle ** 2 * (k @ k)
+    out = np.concatenate([r @ m[:, :3], (m[:, 3] + rng.normal(size=3) * shift)[:, None]], axis=1)
+    return out.T.astype(np.float32).reshape(-1)
+
+
+@pytest.mark.parametrize("moving", [False, True])
+@pytest.mark.parametrize("lanes", [1, 8])
+def test_rolling_shutter_rays_and_samples(env, ref, lanes, moving):
+    """get_xform_given_rolling_shutter (common_device.cuh:401-408; the oracle's restatement is pinned bit for bit against the mount's own function,
+    tests/test_oracle_pins.py): pixel time A + B u + C v + D motionblur_time picks a camera between the view's start and end pose for every ray.
+    moving = False: start == end, non-zero shutter — glm's linear slerp branch, no transcendental, so rays and every sample are bit-exact.
+    moving = True: poses 0.05 rad / 0.02 apart — acos / sin differ in the last ulp between libm and the device: rays to 2e-6."""
+    rng = np.random.default_rng(11)
+    views = []
+    for i, v in enumerate(env["views"]):
+        end = _perturbed_pose(v["xform"], rng, 0.05, 0.02) if moving else None
+        views.append({**v, "xform_end": end, "rolling_shutter": (0.1, 0.2 * (i % 2), 0.5, 0.3)})
+    images, keep = ref.images_from_views(views)
+    pyngp = env["pyngp"]
+    tb = pyngp.Testbed(pyngp.TestbedMode.Nerf)
+    tb.sampler_lanes_per_ray = lanes
+    tb.set_nerf_dataset(views, aabb_scale=1)
+    tb.reload_network_from_json(SMALL_CFG)
+    rpb, max_inf, step = _step_and_capture(tb, ref, env, 2)
+    aabb = ref.make_aabb((0, 0, 0), (1, 1, 1))
+    bf = tb.density_grid(1).cpu().numpy()
+    o = ref.generate_training_samples(rpb, aabb, max_inf, 1337, 1 + step * (1 << 32), images, bf, 0, True, 0.0)
+    c = tb.debug_tensor("counters", torch.int32, 4).cpu().numpy().view(np.uint32)
+    nr = int(o["ray_counter"])
+    assert nr > 100
+    if not moving:
+        assert c[0] == o["ray_counter"] and c[1] == o["numsteps_counter"]
+        assert np.array_equal(tb.debug_tensor("rays", torch.float32, nr * 6).cpu().numpy().reshape(nr, 6), o["rays"][:nr])
+        n_written = int(o["numsteps"][:nr, 0].sum())
+        gcoords = tb.debug_tensor("coords", torch.float32, n_written * 7).cpu().numpy().reshape(n_written, 7)
+        assert np.array_equal(gcoords, o["coords"][:n_written])
+    else:
+        assert abs(int(c[0]) - nr) <= 2                                   # a ray grazing the box may fall either side
+        if int(c[0]) == nr:
+            g = tb.debug_tensor("rays", torch.float32, nr * 6).cpu().numpy().reshape(nr, 6)
+            same = np.array_equal(tb.debug_tensor("ray_indices", torch.int32, nr).cpu().numpy().view(np.uint32), o["ray_indices"][:nr])
+            if same:
+                np.testing.assert_allclose(g, o["rays"][:nr], rtol=0, atol=2e-6)
+    # the shutter matters: the same step without it gives other rays
+    plain, _ = ref.images_from_views(env["views"])
+    o2 = ref.generate_training_samples(rpb, aabb, max_inf, 1337, 1 + step * (1 << 32), plain, bf, 0, True, 0.0)
+    n2 = min(nr, int(o2["ray_counter"]))
+    assert np.abs(o["rays"][:n2] - o2["rays"][:n2]).max() > (1e-3 if moving else 1e-8)
+
+
 FOX_LENS = (0.0578421, -0.0805099, -0.000980296, 0.00015575)          # k1, k2, p1, p2 of data/nerf/fox/transforms.json:6-9
 FOX_PRINCIPAL = (554.558 / 1080.0, 965.268 / 1920.0)                  # cx / w, cy / h (:10-13)
 

@@ -34,8 +34,10 @@ def _load_cpp(L, path, resolutions):
             L.check(lib.ngp_nerf_dataset_set_image(d, i, px.ctypes.data_as(C.c_void_p), 0, w, h))
             v = L.TrainingImage()
             L.check(lib.ngp_nerf_dataset_view(d, i, C.byref(v)))
+            xe, rs = np.zeros(12, np.float32), np.zeros(4, np.float32)
+            L.check(lib.ngp_nerf_dataset_view_motion(d, i, xe.ctypes.data_as(C.c_void_p), rs.ctypes.data_as(C.c_void_p)))
             frames.append(dict(path=buf.value.decode(), xform=np.array(list(v.xform), np.float32), focal=tuple(v.focal_length), pp=tuple(v.principal_point),
-                               lens_mode=v.lens_mode, lens_params=tuple(v.lens_params), res=tuple(v.res)))
+                               lens_mode=v.lens_mode, lens_params=tuple(v.lens_params), res=tuple(v.res), xform_end=xe, rolling_shutter=rs))
         a, s, o, m = C.c_int32(), C.c_float(), (C.c_float * 3)(), C.c_int32()
         L.check(lib.ngp_nerf_dataset_info(d, C.byref(a), C.byref(s), o, C.byref(m)))
         return dict(aabb_scale=a.value, scale=np.float32(s.value), offset=np.array(list(o), np.float32), frames=frames)
@@ -48,6 +50,7 @@ def _compare(cpp, ref, exact_focal=True):
     assert [f["path"] for f in cpp["frames"]] == [f["path"] for f in ref["frames"]]
     for a, b in zip(cpp["frames"], ref["frames"]):
         assert np.array_equal(a["xform"], b["xform"]), (a["path"], a["xform"], b["xform"])         # bit-exact poses
+        assert np.array_equal(a["xform_end"], b["xform_end"]) and np.array_equal(a["rolling_shutter"], np.float32(b["rolling_shutter"]))
         assert a["lens_mode"] == b["lens_mode"] and np.array_equal(np.float32(a["lens_params"]), np.float32(b["lens_params"]))
         assert np.array_equal(np.float32(a["pp"]), np.float32(b["pp"]))
         if exact_focal:
@@ -176,3 +179,20 @@ def test_transparency_rules_and_multiple_json_files(L, tmp_path):
         a_s = C.c_int32(); L.check(lib.ngp_nerf_dataset_info(d, C.byref(a_s), None, None, None)); assert a_s.value == 2
     finally:
         lib.ngp_nerf_dataset_close(d)
+
+
+def test_rolling_shutter_and_start_end_poses(L, tmp_path):
+    """"rolling_shutter" ([A, B, C] or [A, B, C, D], scene level and per frame) and "transform_matrix_start" / "_end" (nerf_loader.cu:190-202,648-649,676-680)"""
+    rng = np.random.default_rng(5)
+    frames = [{"file_path": f"f{i}", "transform_matrix": _pose(rng)} for i in range(4)]
+    frames[1] = {"file_path": "f1", "transform_matrix_start": _pose(rng), "transform_matrix_end": _pose(rng)}
+    frames[2]["rolling_shutter"] = [0.1, 0.0, 0.5, 0.25]                 # per-frame override with a motion-blur term
+    frames[3] = {"file_path": "f3", "transform_matrix_start": _pose(rng)}   # a start pose alone: the end pose is the start pose
+    path = _write_scene(tmp_path, {"camera_angle_x": 0.7, "rolling_shutter": [0.0, 0.0, 1.0]}, frames)
+    cpp, ref = _load_cpp(L, path, (8, 6)), loader_ref.load(path, [(8, 6)] * 4)
+    _compare(cpp, ref, exact_focal=False)
+    f = cpp["frames"]
+    assert np.array_equal(f[0]["rolling_shutter"], np.float32([0, 0, 1, 0])) and np.array_equal(f[0]["xform_end"], f[0]["xform"])
+    assert not np.array_equal(f[1]["xform_end"], f[1]["xform"]) and np.array_equal(f[1]["rolling_shutter"], np.float32([0, 0, 1, 0]))
+    assert np.array_equal(f[2]["rolling_shutter"], np.float32([0.1, 0.0, 0.5, 0.25]))
+    assert np.array_equal(f[3]["xform_end"], f[3]["xform"])

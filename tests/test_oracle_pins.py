@@ -129,3 +129,23 @@ def test_shared_logf_expf_vs_libm(ref):
     assert np.abs(got[~normal].astype(np.float64) - want[~normal].astype(np.float64)).max() <= 2 * 1.4e-45 + 1e-44
     assert l.ref_shared_expf(100.0) == np.inf and l.ref_shared_expf(-200.0) == 0.0 and l.ref_shared_logf(0.0) == -np.inf
     assert np.isnan(l.ref_shared_logf(-1.0)) and l.ref_shared_logf(1.0) == 0.0 and l.ref_shared_expf(0.0) == 1.0
+
+
+def test_rolling_shutter_camera_vs_reference_glm(ref):
+    """get_xform_given_rolling_shutter (common_device.cuh:401-408), the camera EVERY training ray of the reference is built from: position lerp +
+    GLM quat_cast / slerp / normalize / mat3_cast.  tests/golden/rolling_shutter.npz holds the mount's own function (through the mount's GLM) on
+    3000 seeded cases: identical start / end poses (the matrix -> quaternion -> matrix round trip alone moves the rotation by up to 6.6e-7),
+    nearly identical ones (slerp's linear branch) and clearly different ones (acos / sin branch, libm on both sides).  Bit-identical."""
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "rolling_shutter.npz"))
+    l = ref.lib()
+    f32, vp = C.c_float, C.c_void_p
+    l.ref_xform_given_rolling_shutter.argtypes = [vp, vp, vp, f32, f32, f32, vp]
+    l.ref_xform_given_rolling_shutter.restype = None
+    n = len(g["start"])
+    got = np.zeros((n, 12), np.float32)
+    s, e, rs, uvt = (np.ascontiguousarray(g[k]) for k in ("start", "end", "rolling_shutter", "uvt"))
+    for k in range(n):
+        l.ref_xform_given_rolling_shutter(s[k].ctypes.data_as(vp), e[k].ctypes.data_as(vp), rs[k].ctypes.data_as(vp), float(uvt[k, 0]), float(uvt[k, 1]),
+                                          float(uvt[k, 2]), got[k].ctypes.data_as(vp))
+    assert np.array_equal(got.view(np.uint32), g["xform"].view(np.uint32))
+    assert np.abs(got[: n // 3, :9] - s[: n // 3, :9]).max() > 1e-7            # the round trip is not the identity: it is part of the ray

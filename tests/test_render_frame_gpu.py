@@ -103,7 +103,7 @@ def test_ground_truth_frame_matches_restatement(world, case):
     dict(view=2, spp=3, bg=[0.2, 0.6, 0.4, 1.0], exposure=0.5, linear=False, cs=0, curve=1),
     dict(view=5, spp=2, bg=[0.2, 0.6, 0.4, 0.25], exposure=0.0, linear=True, cs=0, curve=3),
 ])
-def test_view_state_render_equals_explicit_camera_plus_output_stage(world, case):
+def test_view_state_render_equals_explicit_camera_plus_output_stage(world, ref, case):
     """set_camera_to_training_view(i) + render(w, h, spp, linear) == the tracer with that view's camera / focal length / principal point
     (explicit-camera entry point, pinned against the oracle tracer elsewhere) followed by the restated accumulate + tonemap"""
     tb, fo = world["tb"], world["fo"]
@@ -114,11 +114,15 @@ def test_view_state_render_equals_explicit_camera_plus_output_stage(world, case)
     try:
         got = tb.render(w, h, case["spp"], case["linear"])
         assert tb.nerf.training.view == case["view"] and tb.render_with_lens_distortion
-        np.testing.assert_allclose(tb.camera_matrix, np.asarray(v["xform"], np.float32).reshape(4, 3).T)
+        # set_camera_to_training_view takes the pose through get_xform_given_rolling_shutter(.., uv = 0.5, t = 0) (testbed.cu:843): the quaternion round trip
+        view_cam = ref.xform_given_rolling_shutter(v["xform"])
+        assert np.array_equal(tb.camera_matrix, view_cam.reshape(4, 3).T)
+        np.testing.assert_allclose(tb.camera_matrix, np.asarray(v["xform"], np.float32).reshape(4, 3).T, atol=2e-6)
     finally:
         tb.background_color = [0, 0, 0, 1]; tb.exposure = 0.0; tb.color_space = 0; tb.tonemap_curve = 0
     meta = {"focal_length": v["focal_length"], "res": (RES, RES), "principal_point": v["principal_point"], "xform": v["xform"]}
     cam, focal, centre = fo.view_of_training_image(meta, w, h)
+    cam = view_cam
     raw = tb.render(w, h, case["spp"], camera_matrix=cam, focal_length=[float(f) for f in focal], screen_center=[float(c) for c in centre])
     want = fo.tonemap_pass(raw, case["exposure"], case["bg"], case["cs"], fo.LINEAR if case["linear"] else fo.SRGB, case["curve"])
     np.testing.assert_allclose(got, want, rtol=1e-4, atol=1e-5)
