@@ -164,6 +164,19 @@ typedef struct ngp_train_stats {   /* Testbed.training_step / .loss / nerf.train
 int ngp_testbed_create(int mode, ngp_testbed_t* out);                                   /* Testbed(mode) python_api.cu:388 */
 void ngp_testbed_destroy(ngp_testbed_t t);
 int ngp_testbed_reload_network_from_json(ngp_testbed_t t, const char* json);            /* python_api.cu:402-407 */
+/* reload_network_from_json(json, config_base_path) (python_api.cu:402-407, testbed.cu:311-316): a config with a "parent" key is an RFC 7386
+ * merge patch over the file <directory of config_base_path>/<parent>, resolved recursively (merge_parent_network_config, testbed.cu:95-106);
+ * name a file, or a directory with a trailing slash */
+int ngp_testbed_reload_network_from_json_base(ngp_testbed_t t, const char* json, const char* config_base_path);
+/* reload_network_from_file(path = "") (python_api.cu:400-401, testbed.cu:228-309): `path` if it exists, else <root_dir>/configs/<nerf|sdf|image>/<path>
+ * for a relative one (find_network_config); JSON with comments; "parent" configs merged; then reset_network.  The path ARGUMENT is remembered
+ * (m_network_config_path, "base.json" at first) and an empty / NULL path reloads it.  ngp_testbed_train on a testbed that has no network yet does
+ * exactly that (testbed.cu:4297-4306).  When "base.json" is not found under root_dir the hyper-parameters of the reference's configs/<mode>/base.json
+ * that are built into the library are used (ngp_builtin_base_config returns that JSON text; mode 0 Nerf, 1 Sdf, 2 Image).  Snapshot files go through
+ * ngp_testbed_load_snapshot.  ngp_testbed_set_root_dir = Testbed.root_dir (python_api.cu:534-537). */
+int ngp_testbed_reload_network_from_file(ngp_testbed_t t, const char* path);
+int ngp_testbed_set_root_dir(ngp_testbed_t t, const char* root_dir);
+int ngp_builtin_base_config(int32_t mode, const char** json);
 /* load_training_data (python_api.cu:398) with in-memory views; uploads pixels host->device */
 int ngp_testbed_set_nerf_dataset(ngp_testbed_t t, void* stream, uint32_t n_images, const ngp_training_image* images, int32_t aabb_scale);
 /* load_training_data(path) for a NeRF scene (python_api.cu:398; load_nerf, src/nerf_loader.cu:259-726): the host side of the loader.
@@ -208,6 +221,16 @@ int ngp_testbed_set_camera_extrinsics_rolling_shutter(ngp_testbed_t t, void* str
 /* Testbed.reset(reset_density_grid) (python_api.cu: reset_network): fresh parameters, optimizer state and counters */
 int ngp_testbed_reset(ngp_testbed_t t, int32_t reset_density_grid);
 int ngp_testbed_set_image(ngp_testbed_t t, void* stream, const float* host_rgba, int32_t width, int32_t height);   /* image mode */
+/* image mode, an 8-bit file as load_stbi_image keeps it (testbed_image.cu:404-418; load_stbi_gpu + from_rgba32, common_device.cu:47-76,
+ * common_device.cuh:771-798): HOST [h][w][4] sRGB bytes with straight alpha become linear, alpha-premultiplied floats on the device */
+int ngp_testbed_set_image_rgba8(ngp_testbed_t t, void* stream, const uint8_t* host_rgba8, int32_t width, int32_t height);
+/* mode_from_scene (common.cu:144-159), what Testbed::load_training_data picks its mode with (testbed.cu:144-150): a directory or *.json ->
+ * 0 Nerf, *.obj / *.stl -> 1 Sdf, *.nvdb -> 3 Volume, any other existing file -> 2 Image, a path that does not exist -> 4 None
+ * (ETestbedMode's values; this library has testbeds for 0, 1 and 2) */
+int ngp_mode_from_scene(const char* path, int32_t* mode);
+/* the mode a snapshot file was saved in (testbed.cu:4950-4955: Testbed::load_snapshot switches to it before it reads anything else);
+ * same values.  No device needed. */
+int ngp_snapshot_mode(const char* path, int32_t* mode);
 /* Sdf mode, Testbed::override_sdf_training_data (python_api.cu:69-99,437): n HOST (point xyz, signed distance) pairs in mesh
  * space; raw_aabb_min/max and mesh_scale are what load_mesh derives from the mesh (m_raw_aabb, m_sdf.mesh_scale) and move the
  * points into the unit cube (pass {0,0,0},{1,1,1},1 for data that is already there).  ngp_testbed_train then runs train_sdf

@@ -92,6 +92,13 @@ SYMBOLS = {
     "ngp_testbed_create": (i32, [i32, C.POINTER(vp)]),
     "ngp_testbed_destroy": (None, [vp]),
     "ngp_testbed_reload_network_from_json": (i32, [vp, cp]),
+    "ngp_testbed_reload_network_from_json_base": (i32, [vp, cp, cp]),
+    "ngp_testbed_reload_network_from_file": (i32, [vp, cp]),
+    "ngp_testbed_set_root_dir": (i32, [vp, cp]),
+    "ngp_builtin_base_config": (i32, [C.c_int32, C.POINTER(cp)]),
+    "ngp_mode_from_scene": (i32, [cp, C.POINTER(C.c_int32)]),
+    "ngp_snapshot_mode": (i32, [cp, C.POINTER(C.c_int32)]),
+    "ngp_testbed_set_image_rgba8": (i32, [vp, vp, vp, C.c_int32, C.c_int32]),
     "ngp_testbed_set_nerf_dataset": (i32, [vp, vp, u32, vp, C.c_int32]),
     "ngp_nerf_dataset_open": (i32, [cp, C.POINTER(vp)]),
     "ngp_nerf_dataset_close": (None, [vp]),

@@ -1,5 +1,6 @@
 // extern "C" boundary (include/ngp_b200.h): operator-level entry points.  Exceptions never cross the ABI — they are
 // caught, stored per thread and reported as a non-zero status + ngp_last_error().
+#include <sys/stat.h>
 #include "../../include/ngp_b200.h"
 #include "testbed.h"
 #include "msgpack_mini.h"
@@ -215,6 +216,26 @@ int ngp_testbed_reload_network_from_json(ngp_testbed_t t, const char* json) {
     t->tb.reload_network_from_json(json);
     NGP_API_END
 }
+int ngp_testbed_reload_network_from_json_base(ngp_testbed_t t, const char* json, const char* config_base_path) {
+    NGP_API_BEGIN require_device(); NGP_CHECK(t && json, "null argument");
+    t->tb.reload_network_from_json(json, config_base_path ? config_base_path : "");
+    NGP_API_END
+}
+int ngp_testbed_reload_network_from_file(ngp_testbed_t t, const char* path) {
+    NGP_API_BEGIN require_device(); NGP_CHECK(t, "null argument");
+    t->tb.reload_network_from_file(path ? path : "");
+    NGP_API_END
+}
+int ngp_testbed_set_root_dir(ngp_testbed_t t, const char* root_dir) {
+    NGP_API_BEGIN NGP_CHECK(t && root_dir, "null argument");
+    t->tb.root_dir = root_dir;
+    NGP_API_END
+}
+int ngp_builtin_base_config(int32_t mode, const char** json) {
+    NGP_API_BEGIN NGP_CHECK(json && mode >= 0 && mode <= 2, "bad argument");
+    *json = ngp::Testbed::builtin_base_config(mode);
+    NGP_API_END
+}
 int ngp_testbed_set_nerf_dataset(ngp_testbed_t t, void* stream, uint32_t n_images, const ngp_training_image* images, int32_t aabb_scale) {
     NGP_API_BEGIN require_device(); NGP_CHECK(t && images, "null argument");
     static_assert(sizeof(ngp_training_image) == sizeof(HostImage), "ABI struct mismatch");
@@ -310,6 +331,33 @@ int ngp_testbed_reset(ngp_testbed_t t, int32_t reset_density_grid) {
 int ngp_testbed_set_image(ngp_testbed_t t, void* stream, const float* rgba, int32_t w, int32_t h) {
     NGP_API_BEGIN require_device(); NGP_CHECK(t && rgba, "null argument");
     t->tb.set_image(S(stream), rgba, w, h);
+    NGP_API_END
+}
+int ngp_testbed_set_image_rgba8(ngp_testbed_t t, void* stream, const uint8_t* rgba8, int32_t w, int32_t h) {
+    NGP_API_BEGIN require_device(); NGP_CHECK(t && rgba8, "null argument");
+    t->tb.set_image_rgba8(S(stream), rgba8, w, h);
+    NGP_API_END
+}
+int ngp_mode_from_scene(const char* path, int32_t* mode) {
+    NGP_API_BEGIN NGP_CHECK(path && mode, "null argument");
+    struct stat st;
+    std::string p = path;
+    while (p.size() > 1 && (p.back() == '/')) p.pop_back();
+    if (stat(p.c_str(), &st) != 0) { *mode = 4; }                     // ETestbedMode::None: the path does not exist
+    else {
+        const size_t slash = p.find_last_of('/'), dot = p.find_last_of('.');
+        std::string ext = (dot != std::string::npos && (slash == std::string::npos || dot > slash)) ? p.substr(dot + 1) : "";
+        for (auto& c : ext) c = (char)tolower((unsigned char)c);
+        if (S_ISDIR(st.st_mode) || ext == "json") *mode = 0;
+        else if (ext == "obj" || ext == "stl") *mode = 1;
+        else if (ext == "nvdb") *mode = 3;
+        else *mode = 2;
+    }
+    NGP_API_END
+}
+int ngp_snapshot_mode(const char* path, int32_t* mode) {
+    NGP_API_BEGIN NGP_CHECK(path && mode, "null argument");
+    *mode = ngp::Testbed::snapshot_mode(path);
     NGP_API_END
 }
 int ngp_testbed_override_sdf_training_data(ngp_testbed_t t, void* stream, const float* points, const float* distances, uint32_t n,

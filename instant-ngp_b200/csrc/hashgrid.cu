@@ -146,7 +146,7 @@ struct LevelCorners {
 template <uint32_t D, uint32_t F>
 __global__ void __launch_bounds__(256) grid_forward_kernel(const GridLayout g, const __half* __restrict__ table, const float* __restrict__ x,
                                                            uint32_t x_stride, uint32_t n, __half* __restrict__ y, int y_layout,
-                                                           const uint32_t* __restrict__ n_dyn) {
+                                                           const uint32_t* __restrict__ n_dyn, const float* __restrict__ max_level) {
     constexpr uint32_t LPC = 8 / F;          // levels per 8-feature chunk
     constexpr uint32_t NC = 1u << D;
     const uint32_t row = blockIdx.x * blockDim.x + threadIdx.x, chunk = blockIdx.y;
@@ -159,10 +159,14 @@ __global__ void __launch_bounds__(256) grid_forward_kernel(const GridLayout g, c
     float acc[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) acc[i] = 0.0f;
+    // per-row level cut-off (GridEncoding::set_max_level_gpu, used by max_level_rand_training): row i keeps the levels below
+    // max_level[i] * n_levels (+1e-3), the others encode to zero
+    const float ml = max_level ? __ldg(max_level + row) * (float)g.n_levels + 1e-3f : 3.0e38f;
 #pragma unroll
     for (uint32_t li = 0; li < LPC; ++li) {
         const uint32_t level = chunk * LPC + li;
         if (level >= g.n_levels) break;
+        if ((float)level >= ml) continue;
         const LevelCorners<D> lc(g, level, xs);
         const typename Feat<F>::T* t = reinterpret_cast<const typename Feat<F>::T*>(table) + g.offsets[level];
         typename Feat<F>::T raw[NC];
@@ -265,7 +269,8 @@ NGP_D void scatter_corners(const LevelCorners<D>& lc, __half* __restrict__ gl, c
 
 template <uint32_t D, uint32_t F>
 __global__ void __launch_bounds__(256) grid_backward_kernel(const GridLayout g, const float* __restrict__ x, uint32_t x_stride, uint32_t n,
-                                                            const __half* __restrict__ dy, int dy_layout, __half* __restrict__ grad, uint32_t chunk0, uint32_t agg_max_runs, bool wide) {
+                                                            const __half* __restrict__ dy, int dy_layout, __half* __restrict__ grad, uint32_t chunk0, uint32_t agg_max_runs, bool wide,
+                                                            const float* __restrict__ max_level) {
     constexpr uint32_t LPC = 8 / F;
     constexpr uint32_t NC = 1u << D;
     const uint32_t row = blockIdx.x * blockDim.x + threadIdx.x, chunk = chunk0 + blockIdx.y, lane = threadIdx.x & 31u;
@@ -274,7 +279,9 @@ __global__ void __launch_bounds__(256) grid_backward_kernel(const GridLayout g, 
     float xs[D];
 #pragma unroll
     for (uint32_t d = 0; d < D; ++d) xs[d] = 0.0f;
+    float ml = 3.0e38f;                       // per-row level cut-off: levels ABOVE max_level * n_levels (+1e-3) receive no gradient from this row
     if (in_range) {
+        if (max_level) ml = __ldg(max_level + row) * (float)g.n_levels + 1e-3f;
         const size_t off = (dy_layout == LAYOUT_BLK8) ? blk8_chunk_offset(row, chunk, g.padded_width) : (size_t)row * g.padded_width + chunk * 8;
         raw = __ldg(reinterpret_cast<const uint4*>(dy + off));
         const float* xp = x + (size_t)row * x_stride;
@@ -289,7 +296,7 @@ __global__ void __launch_bounds__(256) grid_backward_kernel(const GridLayout g, 
         if (level >= g.n_levels) break;
         float d[F]; bool any = false;
 #pragma unroll
-        for (uint32_t f = 0; f < F; ++f) { d[f] = __half2float(dh[li * F + f]); any |= d[f] != 0.0f; }
+        for (uint32_t f = 0; f < F; ++f) { d[f] = (float)level > ml ? 0.0f : __half2float(dh[li * F + f]); any |= d[f] != 0.0f; }
         const uint32_t any_mask = __ballot_sync(0xffffffffu, any);
         if (any_mask == 0u) continue;
         const LevelCorners<D> lc(g, level, xs);
@@ -410,11 +417,11 @@ __global__ void grid_init_kernel(uint64_t n, Pcg32 rng, float* __restrict__ p) {
     } while (0)
 
 void grid_forward(cudaStream_t s, const GridLayout& g, const __half* table, const float* x, uint32_t x_stride, uint32_t n,
-                  __half* y, int y_layout, const uint32_t* n_dyn) {
+                  __half* y, int y_layout, const uint32_t* n_dyn, const float* max_level) {
     if (n == 0) return;
     NGP_PROFILE_SCOPE(s, "grid_forward", n);
     const dim3 blocks(div_round_up(n, 256), g.padded_width / 8, 1);
-    GRID_DISPATCH(grid_forward_kernel, g, table, x, x_stride, n, y, y_layout, n_dyn);
+    GRID_DISPATCH(grid_forward_kernel, g, table, x, x_stride, n, y, y_layout, n_dyn, max_level);
 }
 
 // runs per warp up to which a level is aggregated (0 = never); NGP_AGG_MAX_RUNS overrides for experiments.  Measured (tools/sweep_agg.sh,
@@ -431,21 +438,21 @@ static uint32_t agg_max_runs() {
 }
 
 void grid_backward(cudaStream_t s, const GridLayout& g, const float* x, uint32_t x_stride, uint32_t n, const __half* dy,
-                   int dy_layout, __half* grad) {
+                   int dy_layout, __half* grad, const float* max_level) {
     if (n == 0) return;
     NGP_PROFILE_SCOPE(s, "grid_backward", n);
     const dim3 blocks(div_round_up(n, 256), g.padded_width / 8, 1);
-    GRID_DISPATCH(grid_backward_kernel, g, x, x_stride, n, dy, dy_layout, grad, 0u, agg_max_runs(), red_wide());
+    GRID_DISPATCH(grid_backward_kernel, g, x, x_stride, n, dy, dy_layout, grad, 0u, agg_max_runs(), red_wide(), max_level);
 }
 
 // the same pass restricted to 8-feature chunks [chunk0, chunk0 + n_chunks): the data-parallel step launches it chunk by chunk
 // so that each chunk's slice of the gradient table can be all-reduced while the next chunk is still being scattered
 void grid_backward_chunks(cudaStream_t s, const GridLayout& g, const float* x, uint32_t x_stride, uint32_t n, const __half* dy,
-                          int dy_layout, __half* grad, uint32_t chunk0, uint32_t n_chunks) {
+                          int dy_layout, __half* grad, uint32_t chunk0, uint32_t n_chunks, const float* max_level) {
     if (n == 0 || n_chunks == 0) return;
     NGP_PROFILE_SCOPE(s, "grid_backward", n);
     const dim3 blocks(div_round_up(n, 256), n_chunks, 1);
-    GRID_DISPATCH(grid_backward_kernel, g, x, x_stride, n, dy, dy_layout, grad, chunk0, agg_max_runs(), red_wide());
+    GRID_DISPATCH(grid_backward_kernel, g, x, x_stride, n, dy, dy_layout, grad, chunk0, agg_max_runs(), red_wide(), max_level);
 }
 
 void grid_backward_input(cudaStream_t s, const GridLayout& g, const __half* table, const float* x, uint32_t x_stride,

@@ -93,6 +93,20 @@ void image_eval_coords(cudaStream_t s, uint32_t n, uint32_t offset, const float*
     image_eval_coords_kernel<<<div_round_up(n, 256), 256, 0, s>>>(n, offset, image, W, H, linear_colors, pos, target);
     NGP_POST_LAUNCH();
 }
+// from_rgba32<float> (common_device.cuh:771-798) as load_stbi_gpu calls it (common_device.cu:72: no white/black keying, no mask colour):
+// sRGB bytes with straight alpha -> linear, alpha-premultiplied floats
+__global__ void image_from_rgba8_kernel(uint64_t n, const uint32_t* __restrict__ px, float4* __restrict__ out) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t v = px[i];
+    const float alpha = (float)(v >> 24) * (1.0f / 255.0f);
+    out[i] = make_float4(srgb_to_linear((float)(v & 0xFF) * (1.0f / 255.0f)) * alpha, srgb_to_linear((float)((v >> 8) & 0xFF) * (1.0f / 255.0f)) * alpha,
+                         srgb_to_linear((float)((v >> 16) & 0xFF) * (1.0f / 255.0f)) * alpha, alpha);
+}
+void image_from_rgba8(cudaStream_t s, uint64_t n, const uint8_t* rgba8, float* out) {
+    image_from_rgba8_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(n, (const uint32_t*)rgba8, (float4*)out);
+    NGP_POST_LAUNCH();
+}
 void image_squared_error(cudaStream_t s, uint32_t n, const float* target, const __half* pred, float* se, bool quantize) {
     image_se_kernel<<<div_round_up(n, 256), 256, 0, s>>>(n, target, pred, se, quantize);
     NGP_POST_LAUNCH();

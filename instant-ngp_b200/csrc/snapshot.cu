@@ -213,6 +213,21 @@ static const Json* find_adam(const Json& o, const Json** ema_level) {
     return nullptr;
 }
 
+int Testbed::snapshot_mode(const std::string& path) {
+    std::string bytes = read_file(path);
+    if (ends_with_ci(path, ".ingp")) bytes = zlib_inflate(bytes);
+    Json config = msgpack_decode(bytes.data(), bytes.size());
+    if (!config.contains("snapshot")) throw Error("File '" + path + "' does not contain a snapshot.");
+    const Json& snap = config.at("snapshot");
+    if (!snap.contains("mode")) return MODE_TB_NERF;
+    const std::string mode = to_lower(snap.at("mode").str);
+    if (mode == "nerf") return MODE_TB_NERF;
+    if (mode == "sdf") return MODE_TB_SDF;
+    if (mode == "image") return MODE_TB_IMAGE;
+    if (mode == "volume") return 3;                                  // ETestbedMode::Volume: a mode this library does not implement
+    return 4;                                                        // ETestbedMode::None
+}
+
 void Testbed::load_snapshot(cudaStream_t s, const std::string& path) {
     std::string bytes = read_file(path);
     if (ends_with_ci(path, ".ingp")) bytes = zlib_inflate(bytes);

@@ -1,6 +1,9 @@
 // Host driver (see testbed.h).  Control flow mirrors Testbed::train / train_nerf / train_nerf_step /
 // update_density_grid_nerf / train_image of the reference; the kernels are the sm_100a ones of this library.
 #include "testbed.h"
+#include <fstream>
+#include <sstream>
+#include <sys/stat.h>
 #include <algorithm>
 #include <cmath>
 #include <cstring>
@@ -53,11 +56,83 @@ Testbed::~Testbed() {
     for (void* p : m_image_buffers) cudaFree(p);
 }
 
-void Testbed::reload_network_from_json(const std::string& json) {
-    Json patch = Json::parse(json);
-    if (m_have_config && patch.contains("parent")) m_config.merge_patch(patch); else m_config = patch;   // "parent" merge: testbed.cu:95-106
+static std::string read_text_file(const std::string& path, const char* what) {
+    std::ifstream f(path, std::ios::in | std::ios::binary);
+    if (!f) throw Error(std::string(what) + " '" + path + "' does not exist.");
+    std::stringstream ss; ss << f.rdbuf();
+    return ss.str();
+}
+static bool path_exists(const std::string& p) { struct stat st; return !p.empty() && stat(p.c_str(), &st) == 0; }
+static std::string join_path(const std::string& dir, const std::string& name) { return dir.empty() ? name : (dir.back() == '/' ? dir + name : dir + "/" + name); }
+static std::string dir_of(const std::string& p) { const size_t k = p.find_last_of('/'); return k == std::string::npos ? std::string() : (k == 0 ? std::string("/") : p.substr(0, k)); }
+
+// merge_parent_network_config (testbed.cu:95-106): a config names its "parent" relative to its own directory; the child is an RFC 7386
+// merge patch on top of the (recursively resolved) parent
+static Json merge_parent_network_config(const Json& child, const std::string& child_path, int depth = 0) {
+    if (!child.contains("parent")) return child;
+    NGP_CHECK(depth < 16, "network config: 'parent' chain is too deep (a cycle?)");
+    const std::string parent_path = join_path(dir_of(child_path), child.at("parent").str);
+    Json parent = merge_parent_network_config(Json::parse(read_text_file(parent_path, "Parent network config")), parent_path, depth + 1);
+    parent.merge_patch(child);
+    return parent;
+}
+
+void Testbed::reload_network_from_json(const std::string& json, const std::string& config_base_path) {
+    m_config = merge_parent_network_config(Json::parse(json), config_base_path);
     m_have_config = true;
     reset_network();
+}
+
+static const char* testbed_mode_dir(int mode) { return mode == MODE_TB_NERF ? "nerf" : mode == MODE_TB_SDF ? "sdf" : "image"; }   // to_string(ETestbedMode), common.cu:175-184
+
+// find_network_config (testbed.cu:228-244): the path itself, else <root_dir>/configs/<mode>/<path> for a relative one
+std::string Testbed::find_network_config(const std::string& path) const {
+    if (path_exists(path) || (!path.empty() && path[0] == '/')) return path;
+    const std::string candidate = join_path(join_path(join_path(root_dir, "configs"), testbed_mode_dir(m_mode)), path);   // empty root_dir: ./configs/...
+    return path_exists(candidate) ? candidate : path;
+}
+
+// reload_network_from_file (testbed.cu:275-309) with load_network_config (:246-273) for a *.json config; snapshots go through load_snapshot
+void Testbed::reload_network_from_file(const std::string& path) {
+    if (!path.empty()) {                                                         // :276-286: remember the ARGUMENT ("base.json"), not what it resolved to
+        const std::string candidate = find_network_config(path);
+        if (path_exists(candidate) || !path_exists(network_config_path)) network_config_path = path;
+    }
+    const std::string full = find_network_config(network_config_path);
+    if (path_exists(full)) {
+        m_config = merge_parent_network_config(Json::parse(read_text_file(full, "Network config")), full);
+    } else if (network_config_path == "base.json") {
+        // the reference ships configs/<mode>/base.json beside its binary; a library has no such directory, so the same hyper-parameters are built in
+        m_config = Json::parse(builtin_base_config(m_mode));
+    } else {
+        throw Error("Network config '" + full + "' does not exist.");
+    }
+    m_have_config = true;
+    reset_network();
+}
+
+// The hyper-parameters of the reference's default configs (configs/nerf/base.json, configs/sdf/base.json, configs/image/base.json), restricted to
+// the keys this library reads: the loss, the Ema / ExponentialDecay / Adam chain, the hash grid and the fully fused MLPs.
+const char* Testbed::builtin_base_config(int mode) {
+    if (mode == MODE_TB_NERF)
+        return R"({"loss":{"otype":"Huber"},
+"optimizer":{"otype":"Ema","decay":0.95,"nested":{"otype":"ExponentialDecay","decay_start":20000,"decay_interval":10000,"decay_base":0.33,
+ "nested":{"otype":"Adam","learning_rate":1e-2,"beta1":0.9,"beta2":0.99,"epsilon":1e-15,"l2_reg":1e-6}}},
+"encoding":{"otype":"HashGrid","n_levels":4,"n_features_per_level":4,"log2_hashmap_size":19,"base_resolution":16},
+"network":{"otype":"FullyFusedMLP","activation":"ReLU","output_activation":"None","n_neurons":64,"n_hidden_layers":1},
+"dir_encoding":{"otype":"Composite","nested":[{"n_dims_to_encode":3,"otype":"SphericalHarmonics","degree":4},{"otype":"Identity"}]},
+"rgb_network":{"otype":"FullyFusedMLP","activation":"ReLU","output_activation":"None","n_neurons":64,"n_hidden_layers":2}})";
+    if (mode == MODE_TB_SDF)
+        return R"({"loss":{"otype":"MAPE"},
+"optimizer":{"otype":"Ema","decay":0.95,"nested":{"otype":"ExponentialDecay","decay_start":10000,"decay_interval":5000,"decay_base":0.33,
+ "nested":{"otype":"Adam","learning_rate":1e-4,"beta1":0.9,"beta2":0.99,"epsilon":1e-15,"l2_reg":1e-6}}},
+"encoding":{"otype":"HashGrid","n_levels":16,"n_features_per_level":2,"log2_hashmap_size":19,"base_resolution":16},
+"network":{"otype":"FullyFusedMLP","activation":"ReLU","output_activation":"None","n_neurons":64,"n_hidden_layers":2}})";
+    return R"({"loss":{"otype":"L2"},
+"optimizer":{"otype":"ExponentialDecay","decay_start":20000,"decay_interval":10000,"decay_base":0.33,
+ "nested":{"otype":"Adam","learning_rate":1e-2,"beta1":0.9,"beta2":0.99,"epsilon":1e-15,"l2_reg":1e-6}},
+"encoding":{"otype":"HashGrid","n_levels":16,"n_features_per_level":2,"log2_hashmap_size":24,"base_resolution":16},
+"network":{"otype":"FullyFusedMLP","activation":"ReLU","output_activation":"None","n_neurons":64,"n_hidden_layers":2}})";
 }
 
 // reset_network (testbed.cu:3903-4151): seeds, counters, network + trainer construction, parameter init
@@ -137,16 +212,21 @@ void Testbed::load_nerf_post(cudaStream_t s, int aabb_scale) {
     m_max_cascade = 0;
     while ((1 << m_max_cascade) < aabb_scale) ++m_max_cascade;
     cone_angle_constant = aabb_scale <= 1 ? 0.0f : (1.0f / 256.0f);   // testbed_nerf.cu:3109
-    // density grid: always all 8 mips of bitfield (testbed_nerf.cu:3541-3542)
+    // density grid: always all 8 mips of bitfield (testbed_nerf.cu:3541-3542).  A second scene loaded into a trained testbed (run.py:231 loads the
+    // test transforms that way) keeps the network, the training step and - when the cascade count is unchanged, so that GPUMemory::resize is a
+    // no-op in the reference (testbed_nerf.cu:3417-3420) - the occupancy grid: load_nerf_post (testbed_nerf.cu:3026-3112) resets none of them
     const size_t n_elements = (size_t)NERF_GRID_N_CELLS * (m_max_cascade + 1);
-    NGP_CUDA_CHECK(cudaMemsetAsync(m_density_grid.get<float>(n_elements), 0, n_elements * 4, s));
-    m_density_grid_tmp.get<float>(n_elements);
-    NGP_CUDA_CHECK(cudaMemsetAsync(m_bitfield.get<uint8_t>((size_t)NERF_GRID_N_CELLS * NERF_CASCADES / 8), 0, (size_t)NERF_GRID_N_CELLS * NERF_CASCADES / 8, s));
-    NGP_CUDA_CHECK(cudaMemsetAsync(m_mean.get<float>(4), 0, 16, s));
-    m_partials.get<float>(1024);
-    m_grid_pos.get<float>(n_elements * 3); m_grid_idx.get<uint32_t>(n_elements); m_grid_out.get<__half>(n_elements);
-    m_grid_allocated = true;
-    m_training_step = 0; m_density_grid_ema_step = 0;
+    const bool keep_grid = m_grid_allocated && m_grid_elements == n_elements;
+    if (!keep_grid) {
+        NGP_CUDA_CHECK(cudaMemsetAsync(m_density_grid.get<float>(n_elements), 0, n_elements * 4, s));
+        m_density_grid_tmp.get<float>(n_elements);
+        NGP_CUDA_CHECK(cudaMemsetAsync(m_bitfield.get<uint8_t>((size_t)NERF_GRID_N_CELLS * NERF_CASCADES / 8), 0, (size_t)NERF_GRID_N_CELLS * NERF_CASCADES / 8, s));
+        NGP_CUDA_CHECK(cudaMemsetAsync(m_mean.get<float>(4), 0, 16, s));
+        m_partials.get<float>(1024);
+        m_grid_pos.get<float>(n_elements * 3); m_grid_idx.get<uint32_t>(n_elements); m_grid_out.get<__half>(n_elements);
+        m_grid_allocated = true; m_grid_elements = n_elements;
+        m_density_grid_ema_step = 0;
+    }
     NGP_CUDA_CHECK(cudaStreamSynchronize(s));
 }
 
@@ -240,6 +320,19 @@ void Testbed::set_image(cudaStream_t s, const float* rgba_host, int w, int h) {
     m_image_w = w; m_image_h = h;
 }
 
+// load_stbi_image for an 8-bit file (testbed_image.cu:404-418, load_stbi_gpu common_device.cu:47-76): the decoded bytes go up as they are and
+// become linear premultiplied floats on the device
+void Testbed::set_image_rgba8(cudaStream_t s, const uint8_t* rgba8_host, int w, int h) {
+    NGP_CHECK(m_mode == MODE_TB_IMAGE, "set_image: testbed is not in Image mode");
+    NGP_CHECK(rgba8_host && w > 1 && h > 1, "set_image: bad image");
+    const size_t n = (size_t)w * h;
+    DeviceBuffer bytes;
+    NGP_CUDA_CHECK(cudaMemcpyAsync(bytes.get<uint8_t>(n * 4), rgba8_host, n * 4, cudaMemcpyHostToDevice, s));
+    image_from_rgba8(s, n, bytes.as<uint8_t>(), m_image.get<float>(n * 4));
+    NGP_CUDA_CHECK(cudaStreamSynchronize(s));
+    m_image_w = w; m_image_h = h;
+}
+
 // ---------------------------------------------------------------------------------------------------------------
 // update_density_grid_nerf (testbed_nerf.cu:3412-3536) + training_prep_nerf (:4137-4152)
 // ---------------------------------------------------------------------------------------------------------------
@@ -284,7 +377,8 @@ void Testbed::training_prep_nerf(cudaStream_t s) {
 void Testbed::train(cudaStream_t s, uint32_t batch_size) { train_begin(s, batch_size); train_end(s, 0, 0); }
 
 void Testbed::train_begin(cudaStream_t s, uint32_t batch_size) {
-    NGP_CHECK(m_trainer, "Cannot train without a network: call reload_network_from_json first");
+    if (!m_trainer) reload_network_from_file();          // testbed.cu:4297-4306: training data without an explicitly loaded network -> the default config
+    NGP_CHECK(m_trainer, "Unable to create a neural network trainer.");
     NGP_CHECK(batch_size >= BATCH_GRANULARITY && batch_size % BATCH_GRANULARITY == 0, "training batch size must be a multiple of 256");
     if (m_mode == MODE_TB_NERF) {
         NGP_CHECK(m_n_images > 0, "Cannot train without training data");
@@ -861,7 +955,7 @@ void Testbed::set_nerf_camera_matrix(const float* nerf) {   // NerfDataset::nerf
     for (int c = 0; c < 4; ++c) { camera[c * 3 + 0] = m[c * 3 + 1]; camera[c * 3 + 1] = m[c * 3 + 2]; camera[c * 3 + 2] = m[c * 3 + 0]; }
 }
 void Testbed::set_camera_to_training_view(int v) {
-    NGP_CHECK(m_mode == MODE_TB_NERF && v >= 0 && v < (int)m_n_images, "set_camera_to_training_view: no such training view");
+    NGP_CHECK(m_mode == MODE_TB_NERF && v >= 0 && v < (int)m_host_metas.size(), "set_camera_to_training_view: no such training view");   // views of a snapshot have poses but no pixels
     const ImageMeta& m = m_host_metas[v];
     float old_look_at[3]; for (int k = 0; k < 3; ++k) old_look_at[k] = camera[9 + k] + camera[6 + k] * scale;
     xform_given_rolling_shutter(m.xform, m.xform_end, m.rolling_shutter, 0.5f, 0.5f, 0.0f, camera);   // get_xform_given_rolling_shutter(.., {0.5, 0.5}, 0) (testbed.cu:843)
@@ -937,7 +1031,7 @@ void Testbed::debug_buffer(const std::string& name, void** ptr, uint64_t* bytes)
                        {"mlp_out", &m_mlp_out}, {"dloss", &m_dloss}, {"coords_compacted", &m_coords_compacted}, {"loss", &m_loss},
                        {"grid_pos", &m_grid_pos}, {"grid_idx", &m_grid_idx}, {"grid_out", &m_grid_out}, {"density_grid_tmp", &m_density_grid_tmp},
                        {"mean_density", &m_mean}, {"cam_exposure", &m_cam_exposure}, {"cam_exposure_gradient", &m_cam_exposure_grad}, {"numsteps_all", &m_numsteps_all[k]}, {"image_pos", &m_img_pos}, {"image_target", &m_img_target},
-                       {"image_out", &m_img_out}, {"image_dl", &m_img_dl}, {"sdf_positions", &m_sdf_pos}, {"sdf_distances", &m_sdf_dist}};
+                       {"image_out", &m_img_out}, {"image_dl", &m_img_dl}, {"image", &m_image}, {"sdf_positions", &m_sdf_pos}, {"sdf_distances", &m_sdf_dist}};
     for (const E& e : table) if (name == e.n) { *ptr = e.b->ptr; *bytes = e.b->bytes; return; }
     throw Error("debug_buffer: unknown buffer '" + name + "'");
 }

@@ -30,10 +30,17 @@ public:
     ~Testbed();
 
     // reload_network_from_json (testbed.cu:281-292) -> reset_network (testbed.cu:3903-4151)
-    void reload_network_from_json(const std::string& json);
+    void reload_network_from_json(const std::string& json, const std::string& config_base_path = std::string());
+    // reload_network_from_file / find_network_config (testbed.cu:228-244,275-309): <path>, else <root_dir>/configs/<mode>/<path>; "parent" configs merged
+    void reload_network_from_file(const std::string& path = std::string());
+    std::string find_network_config(const std::string& path) const;
+    static const char* builtin_base_config(int mode);
+    std::string root_dir;                                   // Testbed::m_root_dir (testbed.h:978): where configs/<mode>/ is looked for
+    std::string network_config_path = "base.json";          // Testbed::m_network_config_path (testbed.h:1004)
     // load_training_data equivalents with host buffers (NerfDataset: nerf_loader.h:110-171; load_nerf_post testbed_nerf.cu:3046-3112)
     void set_nerf_dataset(cudaStream_t s, uint32_t n_images, const HostImage* images, int aabb_scale);
     void set_image(cudaStream_t s, const float* rgba_host, int w, int h);
+    void set_image_rgba8(cudaStream_t s, const uint8_t* rgba8_host, int w, int h);
     // override_sdf_training_data (python_api.cu:69-99): n host (point, signed distance) pairs in mesh space, moved into the unit
     // cube with the mesh's raw bounding box and scale; from then on train() runs train_sdf on them (testbed_sdf.cu:1289-1311)
     void override_sdf_training_data(cudaStream_t s, const float* points, const float* distances, uint32_t n, const float* raw_aabb_min,
@@ -90,6 +97,8 @@ public:
     // fp16 density grid, counters, optionally the optimizer state) as MessagePack; ".ingp" = the same inside a zlib stream
     void save_snapshot(cudaStream_t s, const std::string& path, bool include_optimizer_state, bool compress);
     void load_snapshot(cudaStream_t s, const std::string& path);
+    // the "mode" a snapshot file was saved in (MODE_TB_*; testbed.cu:4950-4955: files without the key are NeRF snapshots), read without a testbed
+    static int snapshot_mode(const std::string& path);
 
     TrainStats stats() const;
     Trainer* trainer() { return m_trainer.get(); }
@@ -190,6 +199,7 @@ private:
     std::vector<void*> m_image_buffers; std::vector<size_t> m_image_bytes; DeviceBuffer m_metas; std::vector<ImageMeta> m_host_metas;
     DeviceBuffer m_density_grid, m_density_grid_tmp, m_bitfield, m_mean, m_partials, m_grid_pos, m_grid_idx, m_grid_out;
     uint32_t m_density_grid_ema_step = 0; bool m_grid_allocated = false;
+    size_t m_grid_elements = 0;                             // cells of the occupancy grid as allocated (128^3 x cascades in use)
     float m_ds_scale = 0.33f, m_ds_offset[3] = {0.5f, 0.5f, 0.5f};   // NerfDataset::scale / offset (nerf_loader.h:29, nerf_loader.cu:392-393)
     // NerfCounters (testbed.h:433-447)
     uint32_t m_rays_per_batch = 1u << 12, m_n_rays_total = 0, m_measured = 0, m_measured_before = 0;

@@ -181,6 +181,53 @@ _INT_OPTS = {"loss_type", "rgb_activation", "density_activation", "seed", "sampl
 # enum-valued members (python_api.cu:470,522-523,686): reads come back as the enum
 _ENUM_OPTS = {}     # filled below the enum definitions
 _VECTOR_OPTS = {"screen_center": 2, "relative_focal_length": 2, "up_dir": 3, "background_color": 4}
+# members of Testbed itself, which Testbed::set_mode leaves alone (testbed.cu:178-226 resets m_nerf / m_sdf / m_image and the camera): they may be
+# set before the mode is known and survive a change of mode
+_PERSISTENT_OPTS = {"exposure", "render_mode", "color_space", "tonemap_curve", "snap_to_pixel_centers", "shall_train_encoding", "shall_train_network",
+                    "render_ground_truth", "ground_truth_alpha", "background_color", "seed"}
+
+
+def _default_root_dir():
+    """get_root_dir (common.cu:115-133): the first of ".", ".." that holds a "scripts" directory (the reference also looks beside its executable)"""
+    for d in (".", ".."):
+        if os.path.isdir(os.path.join(d, "scripts")):
+            return d
+    return ""
+
+
+def _loads_with_comments(text):
+    """json::parse(f, nullptr, true, ignore_comments = true) (testbed.cu:268): // and /* */ comments outside strings are skipped"""
+    out, i, n = [], 0, len(text)
+    while i < n:
+        c = text[i]
+        if c == '"':
+            j = i + 1
+            while j < n and text[j] != '"':
+                j += 2 if text[j] == "\\" else 1
+            out.append(text[i:j + 1]); i = j + 1
+        elif text.startswith("//", i):
+            while i < n and text[i] != "\n":
+                i += 1
+        elif text.startswith("/*", i):
+            j = text.find("*/", i + 2)
+            i = n if j < 0 else j + 2
+        else:
+            out.append(c); i += 1
+    return _json.loads("".join(out))
+
+
+def mode_from_scene(path):
+    """mode_from_scene (common.cu:144-159)"""
+    m = C.c_int32()
+    check(lib().ngp_mode_from_scene(os.fspath(path).encode(), C.byref(m)))
+    return TestbedMode(m.value)
+
+
+def builtin_base_config(mode):
+    """the hyper-parameters of the reference's configs/<mode>/base.json as the library carries them (used when no config file is found)"""
+    t = C.c_char_p()
+    check(lib().ngp_builtin_base_config(int(mode), C.byref(t)))
+    return _json.loads(t.value.decode())
 
 
 class RandomMode(enum.IntEnum):       # python_api.cu:299-305
@@ -242,11 +289,15 @@ class _Dataset:
 
 
 class Testbed:
-    def __init__(self, mode=TestbedMode.Nerf, data_path=None, network_config=None):
-        """Testbed(mode) / Testbed(mode, data_path, config_path | json) (python_api.cu:388-390)"""
-        object.__setattr__(self, "_h", C.c_void_p())
-        check(lib().ngp_testbed_create(int(mode), C.byref(self._h)))
-        object.__setattr__(self, "mode", TestbedMode(int(mode)))
+    def __init__(self, mode=TestbedMode.None_, data_path=None, network_config=None):
+        """Testbed() / Testbed(mode) / Testbed(mode, data_path, config_path | json) (python_api.cu:388-390).  Without a mode the testbed is
+        an empty shell, as in the reference (ETestbedMode::None): load_training_data / load_snapshot / load_file pick the mode from what
+        they are given (testbed.cu:144-150,4950-4955) and only then does the library-side testbed exist."""
+        object.__setattr__(self, "_handle", C.c_void_p())
+        object.__setattr__(self, "mode", TestbedMode.None_)
+        object.__setattr__(self, "_explicit", {})                   # every option the user has set: replayed onto the testbed of the next mode
+        object.__setattr__(self, "_root_dir", _default_root_dir())
+        object.__setattr__(self, "_requested_config", None)         # reload_network_from_file before the mode is known (testbed.cu:288-292)
         object.__setattr__(self, "training_batch_size", 1 << 18)    # testbed.h:1005
         object.__setattr__(self, "shall_train", True)
         object.__setattr__(self, "_keep", [])
@@ -262,9 +313,12 @@ class Testbed:
                                "n_images_for_training": _Lazy(self.n_training_views)})
         object.__setattr__(self, "nerf", _Namespace(self, {"rgb_activation": "rgb_activation", "density_activation": "density_activation",
                                                            "cone_angle_constant": "cone_angle_constant",
-                                                           "render_min_transmittance": "render_min_transmittance"}, {"training": training}))
+                                                           "render_min_transmittance": "render_min_transmittance",
+                                                           "render_with_lens_distortion": "render_with_lens_distortion", "sharpen": "nerf_sharpen"},
+                                                    {"training": training}))
         image_training = _Namespace(self, {"snap_to_pixel_centers": "image_snap_to_pixel_centers", "linear_colors": "image_linear_colors"})
         object.__setattr__(self, "image", _Namespace(self, {"random_mode": "image_random_mode"}, {"training": image_training}))
+        self._set_mode(TestbedMode(int(mode)))
         if data_path is not None:
             self.load_training_data(data_path)
         if network_config is not None:
@@ -273,14 +327,47 @@ class Testbed:
             else:
                 self.reload_network_from_file(network_config)
 
+    @property
+    def _h(self):
+        h = self._handle
+        if not h:
+            raise RuntimeError("This testbed has no mode yet: load_training_data / load_snapshot / load_file decide it, or construct Testbed(mode)")
+        return h
+
+    def _set_mode(self, mode):
+        """Testbed::set_mode (testbed.cu:178-226): everything mode-specific (data, network, trainer) is dropped, the options stay."""
+        mode = TestbedMode(int(mode))
+        if mode == self.mode:
+            return
+        if mode == TestbedMode.Volume:
+            raise RuntimeError("Volume mode (NanoVDB scenes) is not part of this library")
+        if self._handle:
+            lib().ngp_testbed_destroy(self._handle)
+            object.__setattr__(self, "_handle", C.c_void_p())
+        object.__setattr__(self, "mode", TestbedMode.None_)
+        object.__setattr__(self, "_dist", None)
+        if mode == TestbedMode.None_:
+            return
+        h = C.c_void_p()
+        check(lib().ngp_testbed_create(int(mode), C.byref(h)))
+        object.__setattr__(self, "_handle", h)
+        object.__setattr__(self, "mode", mode)
+        check(lib().ngp_testbed_set_root_dir(h, os.fspath(self._root_dir).encode()))
+        for name, value in list(self._explicit.items()):
+            setattr(self, name, value)
+        if self._requested_config is not None:
+            req = self._requested_config
+            object.__setattr__(self, "_requested_config", None)
+            self.reload_network_from_file(req)
+
     def __del__(self):
-        h = getattr(self, "_h", None)
+        h = self.__dict__.get("_handle", None)
         if h and lib is not None:     # `lib` is already torn down when the interpreter exits
             try:
                 lib().ngp_testbed_destroy(h)
             except Exception:
                 pass
-            object.__setattr__(self, "_h", None)
+            object.__setattr__(self, "_handle", None)
 
     # ---- runtime knobs (def_readwrite members, python_api.cu:452-537) ----
     def _get_vec(self, name, n):
@@ -295,6 +382,14 @@ class Testbed:
         check(lib().ngp_testbed_set_vector(self._h, name.encode(), (C.c_float * n)(*[float(x) for x in v]), n))
 
     def __getattr__(self, name):
+        if name == "root_dir":               # python_api.cu:534-537
+            return self._root_dir
+        if name == "nerf_sharpen":           # nerf.sharpen (python_api.cu:556): the training images are used as they are
+            return float(self.__dict__.get("_explicit", {}).get(name, 0.0))
+        if name.startswith("_"):
+            raise AttributeError(name)
+        if not self.__dict__.get("_handle") and name in self.__dict__.get("_explicit", {}):
+            return self._explicit[name]
         if name in _VECTOR_OPTS:
             return self._get_vec(name, _VECTOR_OPTS[name])
         if name in ("aabb", "render_aabb"):
@@ -333,6 +428,20 @@ class Testbed:
         return v.value
 
     def __setattr__(self, name, value):
+        if name == "root_dir":
+            object.__setattr__(self, "_root_dir", os.fspath(value))
+            if self._handle:
+                check(lib().ngp_testbed_set_root_dir(self._handle, os.fspath(value).encode()))
+            return
+        if name == "nerf_sharpen":
+            if float(value) != 0.0:
+                raise RuntimeError("nerf.sharpen: sharpening of the training images is not part of this library (leave it at 0)")
+            self._explicit[name] = 0.0
+            return
+        if name in _PERSISTENT_OPTS:
+            self._explicit[name] = value
+            if not self._handle:             # no mode yet: kept, and applied when a mode is chosen
+                return
         if name in _BOOL_OPTS | _FLOAT_OPTS | _INT_OPTS | set(_ENUM_OPTS):
             check(lib().ngp_testbed_set_option(self._h, name.encode(), float(value)))
         elif name == "background_color":     # vec4 in the reference; three components keep the alpha that is set
@@ -437,11 +546,21 @@ class Testbed:
                                                            v.get("rolling_shutter", (0, 0, 0, 0)), convert_to_ngp=False)
 
     def load_training_data(self, path):
-        """Testbed.load_training_data(path) (python_api.cu:398) for a NeRF scene: `path` is a transforms.json, a directory holding
-        *.json files, or a list of either.  The loader logic (frame order, culling, intrinsics, NeRF -> NGP poses) runs in the
+        """Testbed.load_training_data(path) (python_api.cu:398, testbed.cu:135-165).  The mode follows the scene (mode_from_scene): a
+        transforms.json, a directory holding *.json files (or, an extension of this binding, a list of either) is a NeRF scene; any other
+        file is an image to learn in Image mode.  The NeRF loader logic (frame order, culling, intrinsics, NeRF -> NGP poses) runs in the
         library (csrc/nerf_dataset.cu); this binding only decodes the image files it names (OpenCV: png / jpg / exr ...)."""
-        if self.mode != TestbedMode.Nerf:
-            raise RuntimeError("load_training_data: implemented for the Nerf mode (Image: set_image, Sdf: override_sdf_training_data)")
+        first = path if isinstance(path, (str, os.PathLike)) else list(path)[0]
+        scene_mode = mode_from_scene(first)
+        if scene_mode == TestbedMode.None_:
+            raise RuntimeError(f"Data path '{os.fspath(first)}' does not exist.")
+        if scene_mode == TestbedMode.Volume:
+            raise RuntimeError("Volume mode (NanoVDB scenes) is not part of this library")
+        self._set_mode(scene_mode)
+        if scene_mode == TestbedMode.Image:
+            return self._load_image(os.fspath(first))
+        if scene_mode == TestbedMode.Sdf:
+            raise RuntimeError("load_mesh: mesh files are not read by this library; hand the (point, distance) records to override_sdf_training_data")
         import cv2
         paths = []
         for p in ([path] if isinstance(path, (str, os.PathLike)) else list(path)):
@@ -473,6 +592,31 @@ class Testbed:
             check(lib().ngp_testbed_load_nerf_dataset(self._h, _stream(), d))
         finally:
             lib().ngp_nerf_dataset_close(d)
+
+    def _load_image(self, path):
+        """Testbed::load_image (testbed_image.cu:372-437): *.exr and other float formats are kept as they are (linear RGBA), *.bin is the
+        reference's raw dump (int32 height, int32 width, then RGBA halves), everything else is an 8-bit file whose sRGB bytes the library
+        turns into linear premultiplied floats on the device, as load_stbi_gpu does."""
+        if path.lower().endswith(".bin"):
+            with open(path, "rb") as f:
+                h, w = np.frombuffer(f.read(8), np.int32)
+                px = np.frombuffer(f.read(int(h) * int(w) * 8), np.float16).reshape(int(h), int(w), 4).astype(np.float32)
+            return self.set_image(px)
+        import cv2
+        img = cv2.imread(path, cv2.IMREAD_UNCHANGED)
+        if img is None:
+            raise RuntimeError(f"Image file '{path}' could not be read.")
+        if img.ndim == 2:
+            img = np.repeat(img[..., None], 3, axis=2)
+        if img.dtype == np.uint16:
+            img = (img >> 8).astype(np.uint8)
+        is_float = img.dtype != np.uint8
+        if img.shape[2] == 3:
+            img = np.concatenate([img, np.full(img.shape[:2] + (1,), 1.0 if is_float else 255, img.dtype)], axis=2)
+        img = np.ascontiguousarray(img[..., [2, 1, 0, 3]])              # BGRA -> RGBA
+        if is_float:
+            return self.set_image(img.astype(np.float32))
+        check(lib().ngp_testbed_set_image_rgba8(self._h, _stream(), img.ctypes.data_as(C.c_void_p), img.shape[1], img.shape[0]))
 
     def set_training_image(self, frame_idx, pixels):
         """nerf.training.set_image(frame_idx, img) (python_api.cu:49-67): host pixels -> the device copy of one view."""
@@ -529,12 +673,18 @@ class Testbed:
 
     # ---- network ----
     def reload_network_from_json(self, config, config_base_path=""):
+        """python_api.cu:402-407; a config with a "parent" key is merged over <directory of config_base_path>/<parent> (testbed.cu:95-106)"""
         cfg = config if isinstance(config, str) else _json.dumps(config)
-        check(lib().ngp_testbed_reload_network_from_json(self._h, cfg.encode()))
+        check(lib().ngp_testbed_reload_network_from_json_base(self._h, cfg.encode(), os.fspath(config_base_path).encode()))
 
-    def reload_network_from_file(self, path):
-        with open(path) as f:
-            self.reload_network_from_json(f.read())
+    def reload_network_from_file(self, path=""):
+        """python_api.cu:400-401, testbed.cu:275-309: `path`, else <root_dir>/configs/<mode>/<path>; "" reloads the last one ("base.json" at first).
+        Before the mode is known the request is only remembered (:288-292)."""
+        if not self._handle:
+            if path:
+                object.__setattr__(self, "_requested_config", os.fspath(path))
+            return
+        check(lib().ngp_testbed_reload_network_from_file(self._h, os.fspath(path).encode()))
 
     def n_params(self):
         return lib().ngp_testbed_n_params(self._h)
@@ -552,17 +702,54 @@ class Testbed:
         check(lib().ngp_testbed_save_snapshot(self._h, _stream(), os.fspath(path).encode(), int(include_optimizer_state), int(compress)))
 
     def load_snapshot(self, path):
-        check(lib().ngp_testbed_load_snapshot(self._h, _stream(), os.fspath(path).encode()))
+        """Testbed::load_snapshot (testbed.cu:4931-5057): the testbed switches to the mode the snapshot was saved in (:4950-4955)"""
+        p = os.fspath(path)
+        m = C.c_int32()
+        check(lib().ngp_snapshot_mode(p.encode(), C.byref(m)))
+        self._set_mode(TestbedMode(m.value))
+        check(lib().ngp_testbed_load_snapshot(self._h, _stream(), p.encode()))
 
     def load_file(self, path):
-        """Testbed::load_file (testbed.cu:316-370): snapshots by extension, .json as a network config."""
+        """Testbed::load_file (testbed.cu:316-375): snapshots by extension; a *.json is looked into (snapshot / network config / camera
+        path); anything else is training data."""
         p = os.fspath(path)
+        if not os.path.exists(p):
+            if p.lower().endswith(".json") and self._handle:          # a name that resolves under <root_dir>/configs/<mode>/
+                return self.reload_network_from_file(p)
+            raise RuntimeError(f"File '{p}' does not exist.")
         if p.lower().endswith((".ingp", ".msgpack")):
-            self.load_snapshot(p)
-        elif p.lower().endswith(".json"):
-            self.reload_network_from_file(p)
-        else:
-            raise RuntimeError(f"File '{p}' is not a snapshot or network config")
+            return self.load_snapshot(p)
+        if p.lower().endswith(".json"):
+            with open(p) as f:
+                doc = _loads_with_comments(f.read())
+            if "snapshot" in doc:
+                raise RuntimeError("load_file: snapshots in JSON form are not supported; use .ingp / .msgpack")
+            if any(k in doc for k in ("parent", "network", "encoding", "loss", "optimizer")):
+                return self.reload_network_from_file(p)
+            if "path" in doc:
+                return self.load_camera_path(p)
+        self.load_training_data(p)
+        self.shall_train = True
+
+    # ---- what the reference binding has and a headless compute library does not (python_api.cu:408-414,428-445) ----
+    def want_repl(self):
+        return False                         # no window, no key to ask for a REPL with (python_api.cu:413)
+
+    def init_window(self, *args, **kwargs):
+        raise RuntimeError("init_window: the GUI (GLFW / OpenGL) is unavailable on this box; use frame() / train() and render()")
+
+    def init_vr(self):
+        raise RuntimeError("init_vr: OpenXR is unavailable on this box")
+
+    def load_camera_path(self, path):
+        raise RuntimeError("load_camera_path: camera paths (src/camera_path.cu) are not part of this library; "
+                           "set camera_matrix / set_nerf_camera_matrix per frame and call render()")
+
+    def compute_and_save_marching_cubes_mesh(self, *args, **kwargs):
+        raise RuntimeError("compute_and_save_marching_cubes_mesh: marching cubes (src/marching_cubes.cu) is not part of this library")
+
+    def compute_marching_cubes_mesh(self, *args, **kwargs):
+        raise RuntimeError("compute_marching_cubes_mesh: marching cubes (src/marching_cubes.cu) is not part of this library")
 
     # ---- training ----
     def enable_data_parallel(self, process_group=None, native=None):
