@@ -68,6 +68,10 @@ int ngp_encoding_forward(ngp_encoding_t e, void* stream, const void* dev_params_
  * zero it first for Overwrite) */
 int ngp_encoding_backward(ngp_encoding_t e, void* stream, const void* dev_x, uint32_t x_stride, uint32_t n, const void* dev_dy,
                           int dy_layout, void* dev_grad_fp16);
+/* GridEncoding::set_max_level_gpu (tiny-cuda-nn; call sites testbed_nerf.cu:3996,4004,4130): a device array with one float per row for the
+ * forward / backward calls that follow.  Row i encodes the levels l < max_level[i] * n_levels + 1e-3 (the others are zeros) and scatters
+ * gradients to the levels l <= max_level[i] * n_levels + 1e-3.  NULL (the default) = every level. */
+int ngp_encoding_set_max_level_gpu(ngp_encoding_t e, const float* dev_max_level);
 /* Encoding::backward, input gradients (testbed_nerf.cu:2615-2617,4071-4078): dx fp32 [n][n_dims] */
 int ngp_encoding_backward_input(ngp_encoding_t e, void* stream, const void* dev_params_fp16, const void* dev_x, uint32_t x_stride,
                                 uint32_t n, const void* dev_dy, int dy_layout, void* dev_dx);

@@ -89,6 +89,7 @@ SYMBOLS = {
     "ngp_encoded_mlp_inference": (i32, [vp, vp, vp, vp, u32, u32, vp]),
     "ngp_encoded_mlp_forward_backward": (i32, [vp, vp, vp, vp, u32, u32, vp, vp]),
     "ngp_adam_step": (i32, [vp, C.POINTER(AdamHyper), u64, vp, vp, vp, vp, vp, vp, vp, vp]),
+    "ngp_encoding_set_max_level_gpu": (i32, [vp, vp]),
     "ngp_testbed_create": (i32, [i32, C.POINTER(vp)]),
     "ngp_testbed_destroy": (None, [vp]),
     "ngp_testbed_reload_network_from_json": (i32, [vp, cp]),

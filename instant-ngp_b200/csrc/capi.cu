@@ -19,7 +19,7 @@ static thread_local std::string g_last_error;
 
 using namespace ngp;
 
-struct ngp_encoding { GridLayout g; };
+struct ngp_encoding { GridLayout g; const float* max_level = nullptr; };
 struct ngp_nerf_network { NerfNetwork net; explicit ngp_nerf_network(const Json& j) : net(j) {} };
 struct ngp_nerf_dataset { NerfDataset ds; explicit ngp_nerf_dataset(const std::vector<std::string>& p) : ds(p) {} };
 struct ngp_encoded_mlp { EncodedMlp net; ngp_encoded_mlp(const Json& j, uint32_t i, uint32_t o) : net(j, i, o) {} };
@@ -103,12 +103,17 @@ int ngp_encoding_initialize_params(ngp_encoding_t e, void* stream, uint64_t seed
 }
 int ngp_encoding_forward(ngp_encoding_t e, void* stream, const void* params, const void* x, uint32_t x_stride, uint32_t n, void* y, int y_layout) {
     NGP_API_BEGIN require_device(); NGP_CHECK(e && (n == 0 || (params && x && y)), "null argument");
-    grid_forward(S(stream), e->g, H(params), F(x), x_stride, n, H(y), y_layout);
+    grid_forward(S(stream), e->g, H(params), F(x), x_stride, n, H(y), y_layout, nullptr, e->max_level);
     NGP_API_END
 }
 int ngp_encoding_backward(ngp_encoding_t e, void* stream, const void* x, uint32_t x_stride, uint32_t n, const void* dy, int dy_layout, void* grad) {
     NGP_API_BEGIN require_device(); NGP_CHECK(e && (n == 0 || (x && dy && grad)), "null argument");
-    grid_backward(S(stream), e->g, F(x), x_stride, n, H(dy), dy_layout, H(grad));
+    grid_backward(S(stream), e->g, F(x), x_stride, n, H(dy), dy_layout, H(grad), e->max_level);
+    NGP_API_END
+}
+int ngp_encoding_set_max_level_gpu(ngp_encoding_t e, const float* dev_max_level) {
+    NGP_API_BEGIN NGP_CHECK(e, "null argument");
+    e->max_level = dev_max_level;
     NGP_API_END
 }
 int ngp_encoding_backward_input(ngp_encoding_t e, void* stream, const void* params, const void* x, uint32_t x_stride, uint32_t n, const void* dy,
@@ -524,7 +529,7 @@ int ngp_testbed_debug_buffer(ngp_testbed_t t, const char* name, void** ptr, uint
     X(image_snap_to_pixel_centers, bool) X(image_linear_colors, bool) X(image_random_mode, int) X(sampler_lanes_per_ray, uint32_t) X(prefetch_rays, bool) X(prefetch_hits, uint32_t) X(dp_sharded_optimizer, bool) X(device_control_law, bool) \
     X(exposure, float) X(zoom, float) X(scale, float) X(ground_truth_alpha, float) X(render_near_distance, float) X(fov_axis, int) X(training_view, int)                      \
     X(color_space, int) X(tonemap_curve, int) X(render_mode, int) X(render_ground_truth, bool) X(render_with_lens_distortion, bool) X(render_row_stride, int) X(walk_ahead, bool) X(walk_ahead_hits, uint32_t) X(walk_ahead_misses, uint32_t) \
-    X(optimize_exposure, bool) X(exposure_l2_reg, float) X(n_steps_between_cam_updates, uint32_t)
+    X(optimize_exposure, bool) X(exposure_l2_reg, float) X(n_steps_between_cam_updates, uint32_t) X(max_level_rand_training, bool)
 
 int ngp_testbed_set_option(ngp_testbed_t t, const char* name, double value) {
     NGP_API_BEGIN NGP_CHECK(t && name, "null argument");

@@ -455,6 +455,7 @@ __global__ void __launch_bounds__(SCAN_BLOCK) sampler_count_kernel(uint32_t n_ra
         float uv[2]; random_image_pos_training(rng, m.res, snap, uv);
         float texel[4]; read_rgba(m, uv[0], uv[1], texel);
         if (texel[0] >= 0.0f) {   // negative = masked-away pixel (:1430-1435)
+            if (b.max_level_rand) rng.advance(1);             // :1438 the ray's level cut-off (nerf_fill_max_level hands it to the samples)
             const float motionblur_time = rng.next_float();   // :1440
             float xf[12]; xform_given_rolling_shutter(m.xform, m.xform_end, m.rolling_shutter, uv[0], uv[1], motionblur_time, xf);   // :1447-1451
             V3 o, du; uv_to_ray(xf, m.res, m.focal_length, m.principal_point, m.lens_mode, m.lens_params, uv[0], uv[1], o, du);
@@ -701,6 +702,7 @@ __global__ void __launch_bounds__(128) sampler_classify_kernel(uint32_t n_rays, 
         float uv[2]; random_image_pos_training(rng, m.res, snap, uv);
         float texel[4]; read_rgba(m, uv[0], uv[1], texel);
         if (texel[0] >= 0.0f) {   // negative = masked-away pixel (:1430-1435)
+            if (b.max_level_rand) rng.advance(1);             // :1438 the ray's level cut-off (nerf_fill_max_level hands it to the samples)
             const float motionblur_time = rng.next_float();   // :1440
             float xf[12]; xform_given_rolling_shutter(m.xform, m.xform_end, m.rolling_shutter, uv[0], uv[1], motionblur_time, xf);   // :1447-1451
             V3 o, du; uv_to_ray(xf, m.res, m.focal_length, m.principal_point, m.lens_mode, m.lens_params, uv[0], uv[1], o, du);
@@ -964,6 +966,7 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_forward_kernel(uint32_t n_ray
         const uint32_t img = image_idx(ig, n_rays_global, n_images);
         const ImageMeta& m = metas[img];
         float uv[2]; random_image_pos_training(rng, m.res, cfg.snap_to_pixel_centers, uv);
+        const float max_level = cfg.max_level_rand ? rng.next_float() * 2.0f : 1.0f;   // :1775 "Multiply by 2 to ensure 50% of training is at max level"
         rng.advance(1);   // motionblur_time
         V3 bg = ld3(cfg.background_color);
         if (cfg.random_bg_color) { const float a = rng.next_float(), b = rng.next_float(), c = rng.next_float(); bg = v3(a, b, c); }
@@ -987,7 +990,7 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_forward_kernel(uint32_t n_ray
         }
         if (cn == numsteps) rgb_ray = rgb_ray + T * bg;
         float* rs = lb.ray_scratch + (size_t)i * 8;
-        rs[0] = rgb_ray.x; rs[1] = rgb_ray.y; rs[2] = rgb_ray.z; rs[3] = target.x; rs[4] = target.y; rs[5] = target.z; rs[6] = __uint_as_float(img);
+        rs[0] = rgb_ray.x; rs[1] = rgb_ray.y; rs[2] = rgb_ray.z; rs[3] = target.x; rs[4] = target.y; rs[5] = target.z; rs[6] = __uint_as_float(img); rs[7] = max_level;
         lb.compacted_numsteps[i] = cn;
     }
     uint32_t total;
@@ -1028,6 +1031,7 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_backward_kernel(uint32_t n_ra
 #pragma unroll
         for (int k = 0; k < 7; ++k) { c[k] = __ldg(cin + (size_t)j * 7 + k); cout[(size_t)j * 7 + k] = c[k]; }
         if (lb.enc_out) copy_enc_row(lb.enc_in, lb.enc_out, base + j, cbase + j, lb.enc_width);
+        if (lb.max_level_compacted) lb.max_level_compacted[cbase + j] = rs[7];   // :1915-1917
         const V3 pos = unwarp_position(v3(c[0], c[1], c[2]), aabb);
         const float depth = length3(pos - ray_o);
         const float dt = unwarp_dt(c[3]);
@@ -1133,6 +1137,7 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_forward_group_kernel(uint32_t
         const uint32_t img = image_idx(ig, n_rays_global, n_images);
         const ImageMeta& m = metas[img];
         float uv[2]; random_image_pos_training(rng, m.res, cfg.snap_to_pixel_centers, uv);
+        const float max_level = cfg.max_level_rand ? rng.next_float() * 2.0f : 1.0f;   // :1775
         rng.advance(1);
         V3 bg3 = ld3(cfg.background_color);
         if (cfg.random_bg_color) { const float a = rng.next_float(), b = rng.next_float(), c = rng.next_float(); bg3 = v3(a, b, c); }
@@ -1153,7 +1158,7 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_forward_group_kernel(uint32_t
             if (cn == numsteps) ray_c = ray_c + T * bg;
             float* rs = lb.ray_scratch + (size_t)i * 8;
             rs[lane] = ray_c; rs[3 + lane] = target;
-            if (lane == 0) rs[6] = __uint_as_float(img);
+            if (lane == 0) { rs[6] = __uint_as_float(img); rs[7] = max_level; }
         }
         if (lane == 0) lb.compacted_numsteps[i] = cn;
     }
@@ -1207,6 +1212,7 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_backward_group_kernel(uint32_
             const uint2 raw = __ldg(reinterpret_cast<const uint2*>(no + (size_t)j * 4));
             Tb = tb_in[j];
             if (lb.enc_out) copy_enc_row(lb.enc_in, lb.enc_out, base + j, cbase + j, lb.enc_width);
+            if (lb.max_level_compacted) lb.max_level_compacted[cbase + j] = rs[7];
             const V3 pos = unwarp_position(v3(c[0], c[1], c[2]), aabb);
             depth = length3(pos - ray_o);
             dt = unwarp_dt(c[3]);
@@ -1297,10 +1303,31 @@ void nerf_compute_loss(cudaStream_t s, uint32_t n_rays, Aabb aabb, uint32_t n_ra
     NGP_POST_LAUNCH();
 }
 
+// max_level of the un-compacted samples (testbed_nerf.cu:1438,1652-1657), one thread per kept ray: the rng stream of the ray is replayed up to
+// the draw that follows the pixel position
+__global__ void fill_max_level_kernel(Pcg32 rng, uint32_t n_images, const ImageMeta* __restrict__ metas, bool snap, uint32_t ray_offset, uint32_t n_rays_global,
+                                      SamplerBuffers sb, float* __restrict__ max_level) {
+    const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x;
+    if (i >= sb.counters[0]) return;
+    const uint32_t ig = ray_offset + sb.ray_indices[i];
+    rng.advance((int64_t)((uint64_t)ig * N_MAX_RANDOM_SAMPLES_PER_RAY));
+    const ImageMeta& m = metas[image_idx(ig, n_rays_global, n_images)];
+    float uv[2]; random_image_pos_training(rng, m.res, snap, uv);
+    const float v = rng.next_float() * 2.0f;
+    const uint32_t numsteps = sb.numsteps[i * 2 + 0], base = sb.numsteps[i * 2 + 1];
+    for (uint32_t j = 0; j < numsteps; ++j) max_level[base + j] = v;
+}
+void nerf_fill_max_level(cudaStream_t s, uint32_t n_rays_bound, Pcg32 rng, uint32_t n_images, const ImageMeta* metas, bool snap_to_pixel_centers,
+                         uint32_t ray_offset, uint32_t n_rays_global, const SamplerBuffers& sb, float* max_level) {
+    if (n_rays_bound == 0) return;
+    fill_max_level_kernel<<<div_round_up(n_rays_bound, 256), 256, 0, s>>>(rng, n_images, metas, snap_to_pixel_centers, ray_offset, n_rays_global, sb, max_level);
+    NGP_POST_LAUNCH();
+}
+
 // fill_rollover_and_rescale<T> / fill_rollover<T> (tcnn, recalled; testbed_nerf.cu:4061-4069): entries [n_input, n_target) are
 // cyclic copies of [0, n_input); the gradient copies are multiplied by n_input/n_target.
 __global__ void fill_rollover_kernel(uint32_t n_target, const uint32_t* __restrict__ n_input_ptr, __half* __restrict__ dloss, float* __restrict__ coords,
-                                     __half* __restrict__ enc, uint32_t enc_width) {
+                                     __half* __restrict__ enc, uint32_t enc_width, float* __restrict__ max_level) {
     const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x;
     const uint32_t n_input = min(*n_input_ptr, n_target);
     if (i < n_input || i >= n_target || n_input == 0) return;
@@ -1314,10 +1341,11 @@ __global__ void fill_rollover_kernel(uint32_t n_target, const uint32_t* __restri
 #pragma unroll
     for (int k = 0; k < 7; ++k) coords[(size_t)i * 7 + k] = coords[(size_t)src * 7 + k];
     if (enc) copy_enc_row(enc, enc, src, i, enc_width);
+    if (max_level) max_level[i] = max_level[src];   // fill_rollover<float>(.., max_level_compacted) (:4066-4069)
 }
-void nerf_fill_rollover(cudaStream_t s, uint32_t n_target, const uint32_t* n_input_dev, __half* dloss, float* coords, __half* enc, uint32_t enc_width) {
+void nerf_fill_rollover(cudaStream_t s, uint32_t n_target, const uint32_t* n_input_dev, __half* dloss, float* coords, __half* enc, uint32_t enc_width, float* max_level) {
     NGP_PROFILE_SCOPE(s, "fill_rollover", n_target);
-    fill_rollover_kernel<<<div_round_up(n_target, 256), 256, 0, s>>>(n_target, n_input_dev, dloss, coords, enc, enc_width);
+    fill_rollover_kernel<<<div_round_up(n_target, 256), 256, 0, s>>>(n_target, n_input_dev, dloss, coords, enc, enc_width, max_level);
     NGP_POST_LAUNCH();
 }
 

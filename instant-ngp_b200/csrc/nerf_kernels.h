@@ -50,8 +50,15 @@ struct SamplerBuffers {
     // non-null (group marchers only): n_rays / max_samples / scratch_per_ray come from device memory, the n_rays and max_samples
     // arguments of nerf_generate_training_samples are then upper bounds that size the grids
     const StepParams* dyn;
+    // max_level_rand_training (testbed_nerf.cu:1438): every ray that passes the mask test draws one more random number (its level cut-off)
+    // between the pixel position and the motion-blur time, which shifts everything drawn after it
+    uint32_t max_level_rand;
 };
 uint32_t nerf_sampler_lanes_per_ray(uint32_t n_rays);
+// max_level of the un-compacted samples (testbed_nerf.cu:1438,1652-1657): ray i's cut-off = 2 * (the random number after its pixel position), written
+// to max_level[base .. base + numsteps) of the samples the sampler kept for it.  Run behind nerf_generate_training_samples with the same rng.
+void nerf_fill_max_level(cudaStream_t s, uint32_t n_rays_bound, Pcg32 rng, uint32_t n_images, const ImageMeta* metas, bool snap_to_pixel_centers,
+                         uint32_t ray_offset, uint32_t n_rays_global, const SamplerBuffers& sb, float* max_level);
 // The group marchers run in two phases that may be launched apart.  WALK (classify, counting walk with its sample log, scan of the block
 // totals) needs the ray count, the rng and the bitfield but NOT max_samples; EMIT (ray compaction under the max_samples cap, log -> coordinates)
 // is the cheap rest.  The testbed starts the WALK of step N + 2 while step N + 1 is still running (Testbed::launch_walk_ahead).
@@ -71,6 +78,7 @@ struct LossConfig {
     int color_space;                // Testbed::m_color_space: 0 Linear (default) / 1 SRGB selects the target formula (testbed_nerf.cu:1801-1818)
     const float* exposure;          // [n_images][3] per-image exposure in stops (cam_exposure_gpu) or nullptr = all zero (scale exactly 1)
     float* exposure_gradient;       // [n_images][3] accumulated dL/d exposure (optimize_exposure, :1969-1983) or nullptr
+    int max_level_rand;             // max_level_rand_training (:1775): one more draw in the replayed rng stream, the value goes to max_level_compacted
 };
 struct LossBuffers {
     const __half* network_output;   // [*][4]
@@ -83,6 +91,7 @@ struct LossBuffers {
     // optional: encoder outputs of the un-compacted samples (blk8, enc_width columns) are carried along with the samples that
     // survive compaction, so the training forward pass does not gather the hash grid a second time for the same points
     const __half* enc_in; __half* enc_out; uint32_t enc_width;
+    float* max_level_compacted;     // [max_compacted] level cut-off of each kept sample (max_level_rand_training, :1915-1917) or nullptr
 };
 void nerf_compute_loss(cudaStream_t s, uint32_t n_rays, Aabb aabb, uint32_t n_rays_total, Pcg32 rng, uint32_t max_samples_compacted,
                        const LossConfig& cfg, uint32_t n_images, const ImageMeta* metas, const float* mean_density_dev,
@@ -92,7 +101,7 @@ void nerf_compute_loss(cudaStream_t s, uint32_t n_rays, Aabb aabb, uint32_t n_ra
 void nerf_exposure_step(cudaStream_t s, uint32_t n_images, const float* gradient, float* exposure, float* first_moment, float* second_moment, uint32_t iter,
                         float learning_rate, float l2_reg, float per_camera_loss_scale);
 // fill_rollover_and_rescale + fill_rollover (tcnn; testbed_nerf.cu:4061-4069) on dL [n_target][4] fp16 and coords [n_target][7]
-void nerf_fill_rollover(cudaStream_t s, uint32_t n_target, const uint32_t* n_input_dev, __half* dloss, float* coords, __half* enc = nullptr, uint32_t enc_width = 0);
+void nerf_fill_rollover(cudaStream_t s, uint32_t n_target, const uint32_t* n_input_dev, __half* dloss, float* coords, __half* enc = nullptr, uint32_t enc_width = 0, float* max_level_compacted = nullptr);
 // sum of loss[0..n) -> *out_dev (deterministic)
 void reduce_sum_f32(cudaStream_t s, const float* in, uint32_t n, float* out_dev, float* partials /* [1024] */);
 

@@ -93,7 +93,7 @@ void NerfNetwork::initialize_params(uint64_t seed, float* master_dev, cudaStream
 
 void NerfNetwork::inference(cudaStream_t s, const __half* params, const float* coords, uint32_t n, __half* out, const uint32_t* n_dyn) {
     __half* enc = enc_buf.get<__half>((size_t)n * dims.pos_width);
-    grid_forward(s, grid, params + off_grid, coords, 7, n, enc, LAYOUT_BLK8, n_dyn);
+    grid_forward(s, grid, params + off_grid, coords, 7, n, enc, LAYOUT_BLK8, n_dyn, max_level_gpu);
     nerf_mlp_forward(s, dims, params + off_density, params + off_rgb, enc, coords, n, out, n_dyn);
 }
 
@@ -109,10 +109,10 @@ void NerfNetwork::forward_backward(cudaStream_t s, const __half* params, const f
     float* wg = wgrad_buf.get<float>(n_matrix_params);
     NGP_CUDA_CHECK(cudaMemsetAsync(wg, 0, n_matrix_params * sizeof(float), s));
     NGP_CUDA_CHECK(cudaMemsetAsync(grads + off_grid, 0, grid.n_params * sizeof(__half), s));
-    grid_forward(s, grid, params + off_grid, coords, 7, n, enc, LAYOUT_BLK8);
+    grid_forward(s, grid, params + off_grid, coords, 7, n, enc, LAYOUT_BLK8, nullptr, max_level_gpu);
     nerf_mlp_backward(s, dims, params + off_density, params + off_rgb, enc, coords, n, dL_dout, denc, wg);
     cast_f32_to_half(s, wg, grads, n_matrix_params);
-    grid_backward(s, grid, coords, 7, n, denc, LAYOUT_BLK8, grads + off_grid);
+    grid_backward(s, grid, coords, 7, n, denc, LAYOUT_BLK8, grads + off_grid, max_level_gpu);
 }
 
 void NerfNetwork::forward_backward_encoded(cudaStream_t s, const __half* params, const float* coords, uint32_t n, const __half* dL_dout, __half* grads,
@@ -125,7 +125,7 @@ void NerfNetwork::forward_backward_encoded(cudaStream_t s, const __half* params,
     nerf_mlp_backward(s, dims, params + off_density, params + off_rgb, enc, coords, n, dL_dout, denc, wg);
     cast_f32_to_half(s, wg, grads, n_matrix_params);
     if (after_mlp) NGP_CUDA_CHECK(cudaEventRecord(after_mlp, s));
-    if (!slice_ready) { grid_backward(s, grid, coords, 7, n, denc, LAYOUT_BLK8, grads + off_grid); return; }
+    if (!slice_ready) { grid_backward(s, grid, coords, 7, n, denc, LAYOUT_BLK8, grads + off_grid, max_level_gpu); return; }
     // data-parallel step: hand every finished slice of the gradient vector to the caller (who all-reduces it on another stream).
     // The hash-grid pass can be cut into `groups` launches of consecutive level chunks (NGP_DP_SLICES) so that the collective
     // starts under the later chunks.  Measured on 8 B200 (24.4 MB table, all-reduce 0.125 ms): 1 group 0.616 ms/step, 2 groups
@@ -139,7 +139,7 @@ void NerfNetwork::forward_backward_encoded(cudaStream_t s, const __half* params,
     for (uint32_t gi = 0; gi < groups; ++gi) {
         const uint32_t c0 = gi * n_chunks / groups, c1 = (gi + 1) * n_chunks / groups;
         const uint32_t l0 = c0 * levels_per_chunk, l1 = std::min(c1 * levels_per_chunk, grid.n_levels);
-        grid_backward_chunks(s, grid, coords, 7, n, denc, LAYOUT_BLK8, grads + off_grid, c0, c1 - c0);
+        grid_backward_chunks(s, grid, coords, 7, n, denc, LAYOUT_BLK8, grads + off_grid, c0, c1 - c0, max_level_gpu);
         // the MLP weights (first in the vector) travel with the first slice when it starts at level 0: one collective fewer
         const size_t off = off_grid + (size_t)grid.offsets[l0] * grid.n_features, cnt = (size_t)(grid.offsets[l1] - grid.offsets[l0]) * grid.n_features;
         if (gi == 0 && off_grid == n_matrix_params) { (*slice_ready)(0, n_matrix_params + cnt); mlp_sent = true; }

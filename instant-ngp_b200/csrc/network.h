@@ -36,6 +36,9 @@ struct NerfNetwork {
     GridLayout grid; NerfNetDims dims;
     uint64_t off_density = 0, off_rgb = 0, off_grid = 0, n_params = 0, n_matrix_params = 0;
     DeviceBuffer enc_buf, denc_buf, wgrad_buf, enc_train_buf;
+    // GridEncoding::set_max_level_gpu (testbed_nerf.cu:3996,4004,4130): per-row level cut-off of the position encoding for the calls that
+    // follow (one float per sample row; nullptr = all levels).  Used by max_level_rand_training only.
+    const float* max_level_gpu = nullptr;
 
     // config = the reference's network JSON ("encoding", "network", "dir_encoding", "rgb_network")
     explicit NerfNetwork(const Json& config);

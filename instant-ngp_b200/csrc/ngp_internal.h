@@ -35,12 +35,15 @@ void grid_make_layout(GridLayout& g, uint32_t n_dims, uint32_t n_levels, uint32_
 // n_dyn (optional, device memory): the kernels process min(n, *n_dyn) rows; n sizes the launch.  Used by the inference tracer, whose row
 // count per iteration is produced on the device by the ray-compaction kernel
 void grid_forward(cudaStream_t s, const GridLayout& g, const __half* table, const float* x, uint32_t x_stride, uint32_t n,
-                  __half* y, int y_layout, const uint32_t* n_dyn = nullptr);
+                  __half* y, int y_layout, const uint32_t* n_dyn = nullptr, const float* max_level = nullptr);
+// max_level (optional, device memory, one float per row; GridEncoding::set_max_level_gpu of tiny-cuda-nn, recalled - the source is not in
+// the mount): row i encodes only the levels l with l < max_level[i] * n_levels + 1e-3 (the others give zeros) and, backward, scatters
+// gradients only to the levels with l <= max_level[i] * n_levels + 1e-3.  1.0 and above = every level.
 // grad += scatter(w * dy); grad is table-shaped fp16 (caller zeroes it for EGradientMode::Overwrite)
 void grid_backward(cudaStream_t s, const GridLayout& g, const float* x, uint32_t x_stride, uint32_t n, const __half* dy,
-                   int dy_layout, __half* grad);
+                   int dy_layout, __half* grad, const float* max_level = nullptr);
 void grid_backward_chunks(cudaStream_t s, const GridLayout& g, const float* x, uint32_t x_stride, uint32_t n, const __half* dy,
-                          int dy_layout, __half* grad, uint32_t chunk0, uint32_t n_chunks);
+                          int dy_layout, __half* grad, uint32_t chunk0, uint32_t n_chunks, const float* max_level = nullptr);
 // dL/dx [n][n_dims] fp32
 void grid_backward_input(cudaStream_t s, const GridLayout& g, const __half* table, const float* x, uint32_t x_stride,
                          uint32_t n, const __half* dy, int dy_layout, float* dx);

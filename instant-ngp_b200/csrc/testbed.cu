@@ -522,7 +522,7 @@ TrainStats Testbed::stats() const {
 // ---------------------------------------------------------------------------------------------------------------
 Testbed::SamplerKey Testbed::sampler_key(uint32_t n_rays, uint32_t max_inference, uint32_t target) const {
     return {m_training_step, n_rays, max_inference, target, m_rank, m_world, sampler_lanes_per_ray, m_dataset_version, m_rng.state, m_rng.inc,
-            cone_angle_constant, train_snap_to_pixel_centers};
+            cone_angle_constant, train_snap_to_pixel_centers, max_level_rand_training};
 }
 
 SamplerBuffers Testbed::sampler_buffers(cudaStream_t s, uint32_t set, uint32_t target, uint32_t n_rays) {
@@ -530,6 +530,7 @@ SamplerBuffers Testbed::sampler_buffers(cudaStream_t s, uint32_t set, uint32_t t
     const uint32_t max_rays = 1u << 18;
     const uint32_t max_blocks = max_rays / 8 + 1;   // 256 / lanes_per_ray rays per block, lanes_per_ray <= 32
     SamplerBuffers sb{};
+    sb.max_level_rand = max_level_rand_training ? 1u : 0u;
     sb.numsteps_all = m_numsteps_all[set].get<uint32_t>(max_rays); sb.block_steps = m_block_steps[set].get<uint32_t>(max_blocks);
     sb.block_rays = m_block_rays[set].get<uint32_t>(max_blocks); sb.ray_tmp = m_ray_tmp[set].get<float>((size_t)max_rays * 8);
     sb.ray_indices = m_ray_indices[set].get<uint32_t>(max_rays); sb.rays = m_rays[set].get<float>((size_t)max_rays * 6);
@@ -700,13 +701,21 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
     }
     NGP_CUDA_CHECK(cudaMemsetAsync(lb.loss, 0, sizeof(float) * R, s));
     const uint32_t ray_offset = m_rank * R, n_rays_global = m_world * R;
+    float* max_level = nullptr; float* max_level_compacted = nullptr;
+    if (max_level_rand_training) {   // :3996: the inference pass sees each sample with its ray's level cut-off
+        max_level = m_max_level.get<float>(max_samples); max_level_compacted = m_max_level_compacted.get<float>(target);
+        nerf_fill_max_level(s, R, m_rng, m_n_images, m_metas.as<ImageMeta>(), train_snap_to_pixel_centers, ray_offset, n_rays_global, sb, max_level);
+    }
+    m_nerf_net->max_level_gpu = max_level;
     m_nerf_net->inference(s, m_trainer->params, sb.coords, max_inference, mlp_out);   // inference_mixed_precision(.., use_inference_params=false) (:4001)
+    m_nerf_net->max_level_gpu = max_level_compacted;                                  // :4004, for the training pass below
 
     LossConfig lc{};
     lc.loss_type = loss_type; lc.rgb_activation = rgb_activation; lc.density_activation = density_activation;
     lc.random_bg_color = random_bg_color; lc.linear_colors = linear_colors; lc.snap_to_pixel_centers = train_snap_to_pixel_centers;
     memcpy(lc.background_color, background_color, sizeof(lc.background_color));
     lc.loss_scale = LOSS_SCALE; lc.near_distance = near_distance; lc.color_space = color_space;
+    lc.max_level_rand = max_level_rand_training; lb.max_level_compacted = max_level_compacted;
     if (optimize_exposure) ensure_cam_exposure(s);
     if (m_cam_exposure_n == m_n_images && m_n_images) {   // trained (now or earlier): the targets carry the per-image exposure; gradients only while it is being optimised
         lc.exposure = m_cam_exposure.as<float>();
@@ -744,7 +753,7 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
         NGP_CUDA_CHECK(cudaMemcpyAsync(m_host_counters + 5, dc, 8, cudaMemcpyDeviceToHost, m_comm_stream));
         NGP_CUDA_CHECK(cudaEventRecord(m_ev_dp_counters, m_comm_stream));
     }
-    nerf_fill_rollover(s, target, &sb.counters[2], lb.dloss_doutput, lb.coords_compacted, lb.enc_out, lb.enc_width);   // :4061-4069
+    nerf_fill_rollover(s, target, &sb.counters[2], lb.dloss_doutput, lb.coords_compacted, lb.enc_out, lb.enc_width, max_level_compacted);   // :4061-4069
     // forward(compacted) + backward(EGradientMode::Overwrite) (:4077-4078)
     if (m_comm && sharded_step()) {
         // sharded optimizer: ONE in-place reduce-scatter of the whole (padded) gradient vector on the communication stream; Adam on
@@ -771,6 +780,7 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
         m_nerf_net->forward_backward_encoded(s, m_trainer->params, lb.coords_compacted, target, lb.dloss_doutput, m_trainer->grads, m_ev_after_mlp, m_trainer->grid_grads_clean);
     }
     m_trainer->grid_grads_clean = false;
+    m_nerf_net->max_level_gpu = nullptr;   // :4130
     m_rng.advance();   // :4127
     if (early_rays_bound) launch_early_prefetch(s, target, early_rays_bound, early_samples_bound);
 }
@@ -1031,7 +1041,7 @@ void Testbed::debug_buffer(const std::string& name, void** ptr, uint64_t* bytes)
                        {"mlp_out", &m_mlp_out}, {"dloss", &m_dloss}, {"coords_compacted", &m_coords_compacted}, {"loss", &m_loss},
                        {"grid_pos", &m_grid_pos}, {"grid_idx", &m_grid_idx}, {"grid_out", &m_grid_out}, {"density_grid_tmp", &m_density_grid_tmp},
                        {"mean_density", &m_mean}, {"cam_exposure", &m_cam_exposure}, {"cam_exposure_gradient", &m_cam_exposure_grad}, {"numsteps_all", &m_numsteps_all[k]}, {"image_pos", &m_img_pos}, {"image_target", &m_img_target},
-                       {"image_out", &m_img_out}, {"image_dl", &m_img_dl}, {"image", &m_image}, {"sdf_positions", &m_sdf_pos}, {"sdf_distances", &m_sdf_dist}};
+                       {"image_out", &m_img_out}, {"image_dl", &m_img_dl}, {"image", &m_image}, {"max_level", &m_max_level}, {"max_level_compacted", &m_max_level_compacted}, {"sdf_positions", &m_sdf_pos}, {"sdf_distances", &m_sdf_dist}};
     for (const E& e : table) if (name == e.n) { *ptr = e.b->ptr; *bytes = e.b->bytes; return; }
     throw Error("debug_buffer: unknown buffer '" + name + "'");
 }

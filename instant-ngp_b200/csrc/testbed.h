@@ -35,6 +35,9 @@ public:
     void reload_network_from_file(const std::string& path = std::string());
     std::string find_network_config(const std::string& path) const;
     static const char* builtin_base_config(int mode);
+    // Testbed::m_max_level_rand_training (testbed.h:573, python_api.cu:498): every training ray draws a level cut-off 2u, u uniform in [0,1): its samples
+    // are encoded with the hash-grid levels below cut-off * n_levels only (half of the rays keep every level)
+    bool max_level_rand_training = false;
     std::string root_dir;                                   // Testbed::m_root_dir (testbed.h:978): where configs/<mode>/ is looked for
     std::string network_config_path = "base.json";          // Testbed::m_network_config_path (testbed.h:1004)
     // load_training_data equivalents with host buffers (NerfDataset: nerf_loader.h:110-171; load_nerf_post testbed_nerf.cu:3046-3112)
@@ -171,10 +174,10 @@ private:
     void train_image_step(cudaStream_t s, uint32_t batch_size, bool get_loss);                     // testbed_image.cu:214-285
     void train_sdf_step(cudaStream_t s, uint32_t batch_size, bool get_loss);                       // testbed_sdf.cu:1289-1311
     struct SamplerKey {   // everything generate_training_samples depends on besides the bitfield and the view poses
-        uint32_t step, n_rays, max_inference, target, rank, world, lanes, dataset_version; uint64_t rng_state, rng_inc; float cone; bool snap;
+        uint32_t step, n_rays, max_inference, target, rank, world, lanes, dataset_version; uint64_t rng_state, rng_inc; float cone; bool snap, max_level_rand;
         bool operator==(const SamplerKey& o) const {
             return step == o.step && n_rays == o.n_rays && max_inference == o.max_inference && target == o.target && rank == o.rank && world == o.world &&
-                   lanes == o.lanes && dataset_version == o.dataset_version && rng_state == o.rng_state && rng_inc == o.rng_inc && cone == o.cone && snap == o.snap;
+                   lanes == o.lanes && dataset_version == o.dataset_version && rng_state == o.rng_state && rng_inc == o.rng_inc && cone == o.cone && snap == o.snap && max_level_rand == o.max_level_rand;
         }
     };
     SamplerKey sampler_key(uint32_t n_rays, uint32_t max_inference, uint32_t target) const;
@@ -199,6 +202,7 @@ private:
     std::vector<void*> m_image_buffers; std::vector<size_t> m_image_bytes; DeviceBuffer m_metas; std::vector<ImageMeta> m_host_metas;
     DeviceBuffer m_density_grid, m_density_grid_tmp, m_bitfield, m_mean, m_partials, m_grid_pos, m_grid_idx, m_grid_out;
     uint32_t m_density_grid_ema_step = 0; bool m_grid_allocated = false;
+    DeviceBuffer m_max_level, m_max_level_compacted;        // per-sample level cut-offs (max_level_rand_training)
     size_t m_grid_elements = 0;                             // cells of the occupancy grid as allocated (128^3 x cascades in use)
     float m_ds_scale = 0.33f, m_ds_offset[3] = {0.5f, 0.5f, 0.5f};   // NerfDataset::scale / offset (nerf_loader.h:29, nerf_loader.cu:392-393)
     // NerfCounters (testbed.h:433-447)

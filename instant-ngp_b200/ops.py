@@ -73,6 +73,13 @@ class Encoding:
         check(lib().ngp_encoding_initialize_params(self._h, _stream(), seed, _ptr(p)))
         return p
 
+    def set_max_level_gpu(self, max_level):
+        """GridEncoding::set_max_level_gpu: a float32 CUDA tensor with one level cut-off per row for the calls that follow, or None"""
+        if max_level is not None:
+            _dev(max_level, torch.float32)
+        self._max_level = max_level                     # keeps the tensor alive while the library holds its address
+        check(lib().ngp_encoding_set_max_level_gpu(self._h, None if max_level is None else _ptr(max_level)))
+
     def forward(self, params, x, layout=LAYOUT_ROWMAJOR):
         _dev(params, torch.float16); _dev(x, torch.float32)
         n = x.shape[0]

@@ -174,7 +174,7 @@ def _stream():
 
 _BOOL_OPTS = {"random_bg_color", "linear_colors", "snap_to_pixel_centers", "train_snap_to_pixel_centers", "shall_train_encoding", "shall_train_network",
               "image_snap_to_pixel_centers", "image_linear_colors", "image_stratified", "prefetch_rays", "dp_sharded_optimizer", "device_control_law",
-              "render_ground_truth", "render_with_lens_distortion", "walk_ahead", "optimize_exposure"}
+              "render_ground_truth", "render_with_lens_distortion", "walk_ahead", "optimize_exposure", "max_level_rand_training"}
 _FLOAT_OPTS = {"near_distance", "density_grid_decay", "render_min_transmittance", "cone_angle_constant", "exposure", "zoom", "fov", "ground_truth_alpha",
                "render_near_distance", "exposure_l2_reg"}
 _INT_OPTS = {"loss_type", "rgb_activation", "density_activation", "seed", "sampler_lanes_per_ray", "prefetch_hits", "fov_axis", "walk_ahead_hits", "walk_ahead_misses", "n_steps_between_cam_updates"}

@@ -64,6 +64,8 @@ uint64_t ref_grid_layout(const RefGridCfg* cfg, uint32_t* offsets, float* scales
 // per (point, level): 2^D entry indices (level-local, before adding the offset) and weights
 void ref_grid_corners(const RefGridCfg* cfg, const float* x, uint32_t x_stride, uint32_t n, uint32_t level,
                       uint32_t* idx_out, float* w_out);
+// per-row level cut-off for the ref_grid_forward / ref_grid_backward calls that follow (GridEncoding::set_max_level_gpu, recalled); NULL = off
+void ref_grid_set_max_level(const float* max_level);
 // y[n][y_stride] fp16 (columns >= L*F up to y_width are zero-filled)
 void ref_grid_forward(const RefGridCfg* cfg, const uint16_t* table, const float* x, uint32_t x_stride, uint32_t n,
                       uint16_t* y, uint32_t y_stride, uint32_t y_width);
@@ -99,6 +101,9 @@ typedef struct RefNerfNetCfg {
     uint32_t density_hidden;    // n_hidden_layers of density net
     uint32_t rgb_hidden;        // n_hidden_layers of rgb net
 } RefNerfNetCfg;
+// per-sample level cut-offs of the position encoding for the ref_nerf_forward / ref_nerf_backward calls that follow
+// (max_level_rand_training: GridEncoding::set_max_level_gpu, testbed_nerf.cu:3996,4004); NULL = off
+void ref_nerf_set_max_level(const float* max_level);
 uint32_t ref_nerf_pos_width(const RefNerfNetCfg* c);      // padded encoder width (multiple of 16)
 uint64_t ref_nerf_n_params(const RefNerfNetCfg* c, uint64_t* off_density, uint64_t* off_rgb, uint64_t* off_grid);
 // coords: [n][7] float (pos3, dt, dir3) ; out: [n][4] fp16 (r,g,b,sigma raw)

@@ -145,14 +145,23 @@ extern "C" void ref_grid_corners(const RefGridCfg* c, const float* x, uint32_t x
     for (uint32_t i = 0; i < n; ++i) corners(c->n_dims, lv[level], x + (size_t)i * xs, idx_out + (size_t)i * K, w_out + (size_t)i * K);
 }
 
+// GridEncoding::set_max_level_gpu (tiny-cuda-nn grid.h kernel_grid / kernel_grid_backward, RECALLED - the source is not in the mount): with a
+// per-row cut-off m the forward pass writes zeros for the levels l >= m * n_levels + 1e-3 and the backward pass skips the levels
+// l > m * n_levels + 1e-3 (the two comparisons differ in the library).  The pointer applies to the ref_grid_forward / ref_grid_backward calls
+// that follow (rows are indexed from the start of x); NULL = every level.
+static thread_local const float* g_grid_max_level = nullptr;   // thread-local: the per-sample network functions below set it inside their OpenMP loops
+extern "C" void ref_grid_set_max_level(const float* max_level) { g_grid_max_level = max_level; }
+
 extern "C" void ref_grid_forward(const RefGridCfg* c, const uint16_t* table, const float* x, uint32_t xs, uint32_t n,
                                  uint16_t* y, uint32_t ys, uint32_t y_width) {
     std::vector<Level> lv; grid_levels(c, lv);
     const uint32_t D = c->n_dims, F = c->n_features, K = 1u << D;
+    const float* max_level = g_grid_max_level;   // the caller's (the loop's threads have their own thread-local)
     #pragma omp parallel for schedule(static)
     for (int64_t i = 0; i < (int64_t)n; ++i) {
         uint16_t* yo = y + (size_t)i * ys;
         for (uint32_t l = 0; l < c->n_levels; ++l) {
+            if (max_level && (float)l >= max_level[i] * (float)c->n_levels + 1e-3f) { for (uint32_t f = 0; f < F; ++f) yo[l * F + f] = 0; continue; }
             uint32_t idx[8]; float w[8];
             corners(D, lv[l], x + (size_t)i * xs, idx, w);
             const uint16_t* t = table + (size_t)lv[l].offset * F;
@@ -172,6 +181,7 @@ extern "C" void ref_grid_backward(const RefGridCfg* c, const float* x, uint32_t 
     const uint32_t D = c->n_dims, F = c->n_features, K = 1u << D;
     for (uint32_t i = 0; i < n; ++i) {
         for (uint32_t l = 0; l < c->n_levels; ++l) {
+            if (g_grid_max_level && (float)l > g_grid_max_level[i] * (float)c->n_levels + 1e-3f) continue;
             uint32_t idx[8]; float w[8];
             corners(D, lv[l], x + (size_t)i * xs, idx, w);
             double* g = grad + (size_t)lv[l].offset * F;
@@ -376,11 +386,18 @@ extern "C" uint64_t ref_nerf_n_params(const RefNerfNetCfg* c, uint64_t* od, uint
 
 struct NerfSample { float enc[64]; float dact[8 * 128]; float dout[16]; float rin[32]; float ract[8 * 128]; float rout[16]; };
 
-static void nerf_fwd_one(const RefNerfNetCfg* c, const uint16_t* params, const float* coord, NerfSample& S, bool density_only) {
+// per-sample level cut-offs for the ref_nerf_forward / ref_nerf_backward calls that follow (set_max_level_gpu on the position encoding,
+// testbed_nerf.cu:3996,4004); NULL = off.  ref_nerf_density never uses them (the occupancy-grid update runs with the cut-off cleared, :4130).
+static const float* g_nerf_max_level = nullptr;
+extern "C" void ref_nerf_set_max_level(const float* max_level) { g_nerf_max_level = max_level; }
+
+static void nerf_fwd_one(const RefNerfNetCfg* c, const uint16_t* params, const float* coord, NerfSample& S, bool density_only, const float* max_level = nullptr) {
     uint64_t od, orr, og; ref_nerf_n_params(c, &od, &orr, &og);
     uint32_t pw = ref_nerf_pos_width(c);
     uint16_t ench[64];
+    g_grid_max_level = max_level;
     ref_grid_forward(&c->grid, params + og, coord, 7, 1, ench, pw, pw);
+    g_grid_max_level = nullptr;
     for (uint32_t i = 0; i < pw; ++i) S.enc[i] = h2f(ench[i]);
     mlp_fwd_one(params + od, pw, c->width, c->density_hidden, 16, S.enc, S.dout, S.dact);
     if (density_only) return;
@@ -392,7 +409,7 @@ static void nerf_fwd_one(const RefNerfNetCfg* c, const uint16_t* params, const f
 extern "C" void ref_nerf_forward(const RefNerfNetCfg* c, const uint16_t* params, const float* coords, uint32_t n, uint16_t* out) {
     #pragma omp parallel for schedule(static)
     for (int64_t s = 0; s < (int64_t)n; ++s) {
-        NerfSample S; nerf_fwd_one(c, params, coords + (size_t)s * 7, S, false);
+        NerfSample S; nerf_fwd_one(c, params, coords + (size_t)s * 7, S, false, g_nerf_max_level ? g_nerf_max_level + s : nullptr);
         out[s * 4 + 0] = f2h(S.rout[0]); out[s * 4 + 1] = f2h(S.rout[1]); out[s * 4 + 2] = f2h(S.rout[2]);
         out[s * 4 + 3] = f2h(S.dout[0]);
     }
@@ -413,7 +430,7 @@ extern "C" void ref_nerf_backward(const RefNerfNetCfg* c, const uint16_t* params
     uint64_t od, orr, og; ref_nerf_n_params(c, &od, &orr, &og);
     uint32_t pw = ref_nerf_pos_width(c);
     for (uint32_t s = 0; s < n; ++s) {
-        NerfSample S; nerf_fwd_one(c, params, coords + (size_t)s * 7, S, false);
+        NerfSample S; nerf_fwd_one(c, params, coords + (size_t)s * 7, S, false, g_nerf_max_level ? g_nerf_max_level + s : nullptr);
         // extract_rgb (nerf_network.h:45-60,271-275): only rgb channels feed the rgb net
         float g[16] = {0}; for (int i = 0; i < 3; ++i) g[i] = h2f(dL_dout[s * 4 + i]);
         float drin[32];
@@ -424,7 +441,9 @@ extern "C" void ref_nerf_backward(const RefNerfNetCfg* c, const uint16_t* params
         float denc[64];
         mlp_bwd_one(params + od, pw, c->width, c->density_hidden, 16, S.enc, S.dact, gd, denc, grads + od);
         uint16_t dench[64]; for (uint32_t i = 0; i < pw; ++i) dench[i] = f2h(denc[i]);
+        g_grid_max_level = g_nerf_max_level ? g_nerf_max_level + s : nullptr;
         ref_grid_backward(&c->grid, coords + (size_t)s * 7, 7, 1, dench, pw, grads + og);
+        g_grid_max_level = nullptr;
     }
 }
 

@@ -471,6 +471,11 @@ static inline void random_image_pos_training(RefPcg32* rng, const int32_t* res, 
 // (0, 0) = single process.  Mirrors ngp_testbed_set_shard of the CUDA library.
 static uint32_t g_ray_offset = 0, g_n_rays_global = 0;
 extern "C" void ref_set_shard(uint32_t ray_offset, uint32_t n_rays_global) { g_ray_offset = ray_offset; g_n_rays_global = n_rays_global; }
+// max_level_rand_training (testbed.h:573; testbed_nerf.cu:1438,1652-1657,1775,1915-1917): when on, every ray draws a level cut-off 2u between its
+// pixel position and its motion-blur time; the sampler writes it to max_level[base .. base + numsteps) and the loss kernel to
+// max_level_compacted[cbase .. cbase + cn) (either pointer may be NULL)
+static int g_max_level_rand = 0; static float* g_max_level = nullptr; static float* g_max_level_compacted = nullptr;
+extern "C" void ref_set_max_level_rand(int on, float* max_level, float* max_level_compacted) { g_max_level_rand = on; g_max_level = max_level; g_max_level_compacted = max_level_compacted; }
 
 extern "C" void ref_generate_training_samples(uint32_t n_rays, const RefAabb* aabb, uint32_t max_samples, uint32_t n_rays_total,
                                               uint64_t seed, uint64_t skip, uint32_t n_images, const RefImage* images,
@@ -488,7 +493,8 @@ extern "C" void ref_generate_training_samples(uint32_t n_rays, const RefAabb* aa
         float uv[2]; random_image_pos_training(&rng, m->res, snap, uv);
         float texel[4]; read_rgba(m, uv, texel);
         if (texel[0] < 0.0f) continue;                      // masked-away pixel (:1430-1435)
-        const float motionblur_time = ref_pcg32_next_float(&rng);   // :1440; max_level not drawn (rand training off)
+        const float max_level = g_max_level_rand ? ref_pcg32_next_float(&rng) * 2.0f : 1.0f;   // :1438
+        const float motionblur_time = ref_pcg32_next_float(&rng);   // :1440
         RefImage at_t = *m;                                 // the view with the camera of THIS ray (:1447-1451)
         ref_xform_given_rolling_shutter(m->xform, m->xform_end, m->rolling_shutter, uv[0], uv[1], motionblur_time, at_t.xform);
         float ro[3], rd[3]; ref_uv_to_ray(&at_t, uv, ro, rd);
@@ -531,6 +537,7 @@ extern "C" void ref_generate_training_samples(uint32_t n_rays, const RefAabb* aa
                 ++j; t += dt;
             } else t = advance_to_next_voxel(t, cone, pos, d, idir, mip);
         }
+        if (g_max_level_rand && g_max_level) for (j = 0; j < numsteps; ++j) g_max_level[basei + j] = max_level;   // :1652-1657
     }
     out->ray_counter = ray_counter; out->numsteps_counter = numsteps_counter;
 }
@@ -592,6 +599,7 @@ extern "C" void ref_compute_loss(uint32_t n_rays, const RefAabb* aabb, uint32_t 
         uint32_t img = image_idx(ray_idx, n_global, n_images);
         const RefImage* m = &images[img];
         float uv[2]; random_image_pos_training(&rng, m->res, cfg->snap_to_pixel_centers, uv);
+        const float max_level = g_max_level_rand ? ref_pcg32_next_float(&rng) * 2.0f : 1.0f;   // :1775
         ref_pcg32_advance(&rng, 1);   // motionblur_time
         V3 bg = ld3(cfg->background_color);
         if (cfg->random_bg_color) { float a = ref_pcg32_next_float(&rng), b = ref_pcg32_next_float(&rng), c = ref_pcg32_next_float(&rng); bg = v3(a, b, c); }
@@ -634,6 +642,7 @@ extern "C" void ref_compute_loss(uint32_t n_rays, const RefAabb* aabb, uint32_t 
         V3 rgb_ray2 = v3(0, 0, 0); T = 1.f;
         for (uint32_t j = 0; j < cn; ++j) {
             memcpy(out->coords_compacted + (size_t)(cbase + j) * 7, cin + (size_t)j * 7, 7 * sizeof(float));
+            if (g_max_level_rand && g_max_level_compacted) g_max_level_compacted[cbase + j] = max_level;   // :1915-1917
             V3 pos = unwarp_position(ld3(cin + (size_t)j * 7), aabb);
             float depth = length3(pos - ray_o);
             float dt = unwarp_dt(cin[j * 7 + 3]);

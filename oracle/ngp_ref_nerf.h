@@ -88,6 +88,10 @@ void ref_generate_training_samples(uint32_t n_rays, const RefAabb* aabb, uint32_
                                    const uint8_t* bitfield, uint32_t max_mip, int snap_to_pixel_centers,
                                    float cone_angle_constant, RefSamplerOut* out);
 
+// max_level_rand_training (testbed_nerf.cu:1438,1652-1657,1775,1915-1917): a process-wide switch for the two functions around this line; the
+// level cut-offs go to max_level [max_samples] / max_level_compacted [max_compacted] when the pointers are not NULL
+void ref_set_max_level_rand(int on, float* max_level, float* max_level_compacted);
+
 // --- loss + compositor + gradient (testbed_nerf.cu:186-283,317-387,1340-1355,1660-2012) ---
 typedef struct RefLossCfg {
     int loss_type, rgb_activation, density_activation;

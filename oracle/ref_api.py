@@ -134,16 +134,31 @@ def grid_corners(cfg, x, level):
     return idx, w
 
 
-def grid_forward(cfg, table_h, x, width):
+def _with_max_level(setter, max_level, call):
+    """run `call` with the per-row level cut-offs installed (GridEncoding::set_max_level_gpu), and clear them again"""
+    if max_level is None:
+        return call()
+    ml = np.ascontiguousarray(max_level, np.float32)
+    fn = getattr(lib(), setter); fn.argtypes = [vp]; fn.restype = None
+    fn(P(ml))
+    try:
+        return call()
+    finally:
+        fn(None)
+
+
+def grid_forward(cfg, table_h, x, width, max_level=None):
     n = x.shape[0]
     y = np.zeros((n, width), np.float16)
-    lib().ref_grid_forward(C.byref(cfg), P(table_h), P(x), u32(x.shape[1]), u32(n), P(y), u32(width), u32(width))
+    _with_max_level("ref_grid_set_max_level", max_level,
+                    lambda: lib().ref_grid_forward(C.byref(cfg), P(table_h), P(x), u32(x.shape[1]), u32(n), P(y), u32(width), u32(width)))
     return y
 
 
-def grid_backward(cfg, x, dy, n_params):
+def grid_backward(cfg, x, dy, n_params, max_level=None):
     g = np.zeros(n_params, np.float64)
-    lib().ref_grid_backward(C.byref(cfg), P(x), u32(x.shape[1]), u32(x.shape[0]), P(dy), u32(dy.shape[1]), P(g))
+    _with_max_level("ref_grid_set_max_level", max_level,
+                    lambda: lib().ref_grid_backward(C.byref(cfg), P(x), u32(x.shape[1]), u32(x.shape[0]), P(dy), u32(dy.shape[1]), P(g)))
     return g
 
 
@@ -182,9 +197,10 @@ def nerf_init(cfg, seed=1337):
     return p
 
 
-def nerf_forward(cfg, params_h, coords):
+def nerf_forward(cfg, params_h, coords, max_level=None):
     out = np.zeros((coords.shape[0], 4), np.float16)
-    lib().ref_nerf_forward(C.byref(cfg), P(params_h), P(coords), u32(coords.shape[0]), P(out))
+    _with_max_level("ref_nerf_set_max_level", max_level,
+                    lambda: lib().ref_nerf_forward(C.byref(cfg), P(params_h), P(coords), u32(coords.shape[0]), P(out)))
     return out
 
 
@@ -194,9 +210,10 @@ def nerf_density(cfg, params_h, pos):
     return out
 
 
-def nerf_backward(cfg, params_h, coords, dL_h):
+def nerf_backward(cfg, params_h, coords, dL_h, max_level=None):
     g = np.zeros(nerf_n_params(cfg)[0], np.float64)
-    lib().ref_nerf_backward(C.byref(cfg), P(params_h), P(coords), u32(coords.shape[0]), P(dL_h), P(g))
+    _with_max_level("ref_nerf_set_max_level", max_level,
+                    lambda: lib().ref_nerf_backward(C.byref(cfg), P(params_h), P(coords), u32(coords.shape[0]), P(dL_h), P(g)))
     return g
 
 
@@ -260,24 +277,46 @@ def update_bitfield(grid, n_cascades):
     return bf, float(mean)
 
 
-def generate_training_samples(n_rays, aabb, max_samples, seed, skip, images, bitfield, max_mip, snap, cone):
+def _max_level_rand(on, max_level=None, max_level_compacted=None):
+    fn = lib().ref_set_max_level_rand; fn.argtypes = [C.c_int, vp, vp]; fn.restype = None
+    fn(int(on), None if max_level is None else P(max_level), None if max_level_compacted is None else P(max_level_compacted))
+
+
+def generate_training_samples(n_rays, aabb, max_samples, seed, skip, images, bitfield, max_mip, snap, cone, max_level_rand=False):
+    """max_level_rand (max_level_rand_training): one more draw per ray; the result then carries max_level [max_samples]"""
     out = SamplerOut()
     ray_indices = np.zeros(n_rays, np.uint32); rays = np.zeros((n_rays, 6), np.float32); numsteps = np.zeros((n_rays, 2), np.uint32)
     coords = np.zeros((max_samples, 7), np.float32)
     out.ray_indices, out.rays, out.numsteps, out.coords = P(ray_indices).value, P(rays).value, P(numsteps).value, P(coords).value
-    lib().ref_generate_training_samples(u32(n_rays), C.byref(aabb), u32(max_samples), u32(0), u64(seed), u64(skip), u32(len(images)), images,
-                                        P(bitfield), u32(max_mip), i32(int(snap)), f32(cone), C.byref(out))
-    return dict(ray_indices=ray_indices, rays=rays, numsteps=numsteps, coords=coords, ray_counter=out.ray_counter, numsteps_counter=out.numsteps_counter)
+    max_level = np.ones(max_samples, np.float32) if max_level_rand else None
+    _max_level_rand(max_level_rand, max_level)
+    try:
+        lib().ref_generate_training_samples(u32(n_rays), C.byref(aabb), u32(max_samples), u32(0), u64(seed), u64(skip), u32(len(images)), images,
+                                            P(bitfield), u32(max_mip), i32(int(snap)), f32(cone), C.byref(out))
+    finally:
+        _max_level_rand(False)
+    r = dict(ray_indices=ray_indices, rays=rays, numsteps=numsteps, coords=coords, ray_counter=out.ray_counter, numsteps_counter=out.numsteps_counter)
+    if max_level_rand:
+        r["max_level"] = max_level
+    return r
 
 
-def compute_loss(n_rays, aabb, seed, skip, max_compacted, rays_counter, cfg, images, net_out_h, ray_indices, rays, numsteps, coords):
+def compute_loss(n_rays, aabb, seed, skip, max_compacted, rays_counter, cfg, images, net_out_h, ray_indices, rays, numsteps, coords, max_level_rand=False):
     out = LossOut()
     dloss = np.zeros((max_compacted, 4), np.float16); cc = np.zeros((max_compacted, 7), np.float32); loss = np.zeros(n_rays, np.float32)
     ns = numsteps.copy(); rgb_ray = np.zeros((n_rays, 3), np.float32)
     out.dloss_doutput, out.coords_compacted, out.loss, out.numsteps, out.rgb_ray = P(dloss).value, P(cc).value, P(loss).value, P(ns).value, P(rgb_ray).value
-    lib().ref_compute_loss(u32(n_rays), C.byref(aabb), u32(0), u64(seed), u64(skip), u32(max_compacted), u32(rays_counter), C.byref(cfg),
-                           u32(len(images)), images, P(net_out_h), P(ray_indices), P(rays), P(coords), C.byref(out))
-    return dict(dloss=dloss, coords_compacted=cc, loss=loss, numsteps=ns, rgb_ray=rgb_ray, compacted_counter=out.compacted_counter)
+    mlc = np.ones(max_compacted, np.float32) if max_level_rand else None
+    _max_level_rand(max_level_rand, None, mlc)
+    try:
+        lib().ref_compute_loss(u32(n_rays), C.byref(aabb), u32(0), u64(seed), u64(skip), u32(max_compacted), u32(rays_counter), C.byref(cfg),
+                               u32(len(images)), images, P(net_out_h), P(ray_indices), P(rays), P(coords), C.byref(out))
+    finally:
+        _max_level_rand(False)
+    r = dict(dloss=dloss, coords_compacted=cc, loss=loss, numsteps=ns, rgb_ray=rgb_ray, compacted_counter=out.compacted_counter)
+    if max_level_rand:
+        r["max_level_compacted"] = mlc
+    return r
 
 
 def xform_given_rolling_shutter(start, end=None, rolling_shutter=(0, 0, 0, 0), u=0.5, v=0.5, motionblur_time=0.0):
