@@ -196,6 +196,12 @@ void ngp_nerf_dataset_close(ngp_nerf_dataset_t d);
 uint32_t ngp_nerf_dataset_n_images(ngp_nerf_dataset_t d);
 int ngp_nerf_dataset_image_path(ngp_nerf_dataset_t d, uint32_t i, char* buf, uint64_t buf_size);
 int ngp_nerf_dataset_set_image(ngp_nerf_dataset_t d, uint32_t i, const void* host_pixels, int32_t data_type, int32_t width, int32_t height);
+/* depth supervision data (nerf_loader.cu:471-473,609-621,711): with "integer_depth_scale" in the scene json a frame may name a "depth_path", a
+ * 16-bit single-channel image of the view's resolution.  ngp_nerf_dataset_depth_path gives the resolved path ("" = nothing to read for this frame);
+ * the caller decodes it and hands the [h][w] uint16 pixels over (after the frame's ngp_nerf_dataset_set_image).  ngp_testbed_load_nerf_dataset
+ * uploads value * integer_depth_scale * scene scale per pixel. */
+int ngp_nerf_dataset_depth_path(ngp_nerf_dataset_t d, uint32_t i, char* buf, uint64_t buf_size);
+int ngp_nerf_dataset_set_depth(ngp_nerf_dataset_t d, uint32_t i, const uint16_t* host_pixels, int32_t width, int32_t height);
 /* scene-level results: aabb_scale, scale, offset[3], from_mitsuba */
 int ngp_nerf_dataset_info(ngp_nerf_dataset_t d, int32_t* aabb_scale, float* scale, float* offset3, int32_t* from_mitsuba);
 /* view i as it will be uploaded (pixels point into the dataset's own copy; focal length valid after set_image) */
@@ -222,6 +228,11 @@ int ngp_testbed_set_camera_extrinsics(ngp_testbed_t t, void* stream, int32_t fra
  * position linearly, rotation by quaternion slerp).  The loader sets both from "transform_matrix_start" / "_end" and "rolling_shutter". */
 int ngp_testbed_set_camera_extrinsics_rolling_shutter(ngp_testbed_t t, void* stream, int32_t frame_idx, const float* camera_to_world_start,
                                                       const float* camera_to_world_end, const float* rolling_shutter4, int32_t convert_to_ngp);
+/* the depth half of NerfDataset::set_training_image (nerf_loader.cu:907-959; nerf.training.set_image(frame_idx, img, depth_img, depth_scale),
+ * python_api.cu:49-67): HOST depth map of view frame_idx, [h][w] uint16 (depth_type 0) or float32 (1), kept on the device as value * depth_scale
+ * (scene units along the view axis).  NULL or depth_scale == 0: a map of zeros (no supervision from this view); depth_scale < 0: the view's map is
+ * dropped.  Used by the loss when the option depth_supervision_lambda > 0 (testbed_nerf.cu:1848-1856,1934-1939; depth_loss_type, L1 by default). */
+int ngp_testbed_set_training_depth(ngp_testbed_t t, void* stream, int32_t frame_idx, const void* host_depth, int32_t depth_type, float depth_scale);
 /* Testbed.reset(reset_density_grid) (python_api.cu: reset_network): fresh parameters, optimizer state and counters */
 int ngp_testbed_reset(ngp_testbed_t t, int32_t reset_density_grid);
 int ngp_testbed_set_image(ngp_testbed_t t, void* stream, const float* host_rgba, int32_t width, int32_t height);   /* image mode */

@@ -263,6 +263,18 @@ int ngp_nerf_dataset_image_path(ngp_nerf_dataset_t d, uint32_t i, char* buf, uin
     memcpy(buf, p.c_str(), p.size() + 1);
     NGP_API_END
 }
+int ngp_nerf_dataset_depth_path(ngp_nerf_dataset_t d, uint32_t i, char* buf, uint64_t buf_size) {
+    NGP_API_BEGIN NGP_CHECK(d && buf && buf_size > 0, "null argument"); NGP_CHECK(i < d->ds.n_images(), "Invalid frame index");
+    const std::string& p = d->ds.frames[i].depth_path;
+    NGP_CHECK(p.size() + 1 <= buf_size, "depth_path: buffer too small");
+    memcpy(buf, p.c_str(), p.size() + 1);
+    NGP_API_END
+}
+int ngp_nerf_dataset_set_depth(ngp_nerf_dataset_t d, uint32_t i, const uint16_t* pixels, int32_t w, int32_t h) {
+    NGP_API_BEGIN NGP_CHECK(d, "null argument");
+    d->ds.set_depth(i, pixels, w, h);
+    NGP_API_END
+}
 int ngp_nerf_dataset_set_image(ngp_nerf_dataset_t d, uint32_t i, const void* pixels, int32_t data_type, int32_t w, int32_t h) {
     NGP_API_BEGIN NGP_CHECK(d, "null argument");
     d->ds.set_image(i, pixels, data_type, w, h);
@@ -303,6 +315,10 @@ int ngp_testbed_load_nerf_dataset(ngp_testbed_t t, void* stream, ngp_nerf_datase
         const bool moving = memcmp(f.xform, f.xform_end, sizeof(f.xform)) != 0;
         const bool shutter = f.rolling_shutter[0] != 0.f || f.rolling_shutter[1] != 0.f || f.rolling_shutter[2] != 0.f || f.rolling_shutter[3] != 0.f;
         if (moving || shutter) t->tb.set_camera_extrinsics_rolling_shutter(S(stream), (int)i, f.xform, f.xform_end, f.rolling_shutter, false);
+        // depth maps in scene units: integer_depth_scale * scene scale (nerf_loader.cu:711); a data set with a depth scale gives EVERY view a map
+        // (zeros where a frame names no depth file)
+        const float depth_scale = f.depth_scale * d->ds.scale;
+        if (depth_scale >= 0.f) t->tb.set_training_depth(S(stream), (int)i, f.depth_pixels.empty() ? nullptr : f.depth_pixels.data(), 0, depth_scale);
     }
     NGP_API_END
 }
@@ -326,6 +342,11 @@ int ngp_testbed_set_camera_extrinsics_rolling_shutter(ngp_testbed_t t, void* str
 int ngp_testbed_set_camera_extrinsics(ngp_testbed_t t, void* stream, int32_t frame_idx, const float* c2w, int32_t convert_to_ngp) {
     NGP_API_BEGIN require_device(); NGP_CHECK(t && c2w, "null argument");
     t->tb.set_camera_extrinsics(S(stream), frame_idx, c2w, convert_to_ngp != 0);
+    NGP_API_END
+}
+int ngp_testbed_set_training_depth(ngp_testbed_t t, void* stream, int32_t frame_idx, const void* host_depth, int32_t depth_type, float depth_scale) {
+    NGP_API_BEGIN require_device(); NGP_CHECK(t, "null argument");
+    t->tb.set_training_depth(S(stream), frame_idx, host_depth, depth_type, depth_scale);
     NGP_API_END
 }
 int ngp_testbed_reset(ngp_testbed_t t, int32_t reset_density_grid) {
@@ -529,7 +550,7 @@ int ngp_testbed_debug_buffer(ngp_testbed_t t, const char* name, void** ptr, uint
     X(image_snap_to_pixel_centers, bool) X(image_linear_colors, bool) X(image_random_mode, int) X(sampler_lanes_per_ray, uint32_t) X(prefetch_rays, bool) X(prefetch_hits, uint32_t) X(dp_sharded_optimizer, bool) X(device_control_law, bool) \
     X(exposure, float) X(zoom, float) X(scale, float) X(ground_truth_alpha, float) X(render_near_distance, float) X(fov_axis, int) X(training_view, int)                      \
     X(color_space, int) X(tonemap_curve, int) X(render_mode, int) X(render_ground_truth, bool) X(render_with_lens_distortion, bool) X(render_row_stride, int) X(walk_ahead, bool) X(walk_ahead_hits, uint32_t) X(walk_ahead_misses, uint32_t) \
-    X(optimize_exposure, bool) X(exposure_l2_reg, float) X(n_steps_between_cam_updates, uint32_t) X(max_level_rand_training, bool)
+    X(optimize_exposure, bool) X(exposure_l2_reg, float) X(n_steps_between_cam_updates, uint32_t) X(max_level_rand_training, bool) X(depth_supervision_lambda, float) X(depth_loss_type, int)
 
 int ngp_testbed_set_option(ngp_testbed_t t, const char* name, double value) {
     NGP_API_BEGIN NGP_CHECK(t && name, "null argument");

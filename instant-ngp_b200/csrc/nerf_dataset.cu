@@ -138,6 +138,7 @@ NerfDataset::NerfDataset(const std::vector<std::string>& json_paths) {
     }
     size_t total = 0; for (auto& k : kept) total += k.size();
     if (total == 0) throw Error("No training images were found for NeRF training!");
+    bool enable_depth_loading = true; float depth_scale = -1.f;   // persist from one json to the next, like the transparency flags (:283-285,404)
     // pass 2 (nerf_loader.cu:405-700): scene-level fields, then per-frame lens / pose
     for (size_t ji = 0; ji < m_jsons.size(); ++ji) {
         const Json& json = m_jsons[ji];
@@ -151,6 +152,8 @@ NerfDataset::NerfDataset(const std::vector<std::string>& json_paths) {
         if (json.contains("white_transparent")) white_transparent = json.value("white_transparent", false);
         if (json.contains("black_transparent")) black_transparent = json.value("black_transparent", false);
         if (json.contains("scale")) scale = num(json.at("scale"));
+        if (json.contains("enable_depth_loading")) enable_depth_loading = json.value("enable_depth_loading", true);   // :420-423
+        if (json.contains("integer_depth_scale")) depth_scale = num(json.at("integer_depth_scale"));                  // :471-473
         LensState lens;
         read_lens(json, lens);
         if (json.contains("aabb_scale")) aabb_scale = (int)num(json.at("aabb_scale"));
@@ -172,6 +175,11 @@ NerfDataset::NerfDataset(const std::vector<std::string>& json_paths) {
             d.json_index = ji; d.frame_index = fi; d.white_transparent = white_transparent; d.black_transparent = black_transparent;
             d.file_path = fr.at("file_path").str;
             d.resolved_path = resolve_path(base, d.file_path);
+            d.depth_scale = depth_scale;
+            if (enable_depth_loading && depth_scale > 0.f && fr.contains("depth_path")) {   // :609-621
+                const std::string dp = resolve_path(base, fr.at("depth_path").str);
+                if (file_exists(dp)) d.depth_path = dp;
+            }
             const Json& mat = fr.contains("transform_matrix_start") ? fr.at("transform_matrix_start") : fr.at("transform_matrix");
             const Json& mat_end = fr.contains("transform_matrix_end") ? fr.at("transform_matrix_end") : mat;   // :648-649
             for (int m = 0; m < 3; ++m) for (int n = 0; n < 4; ++n) { d.xform_nerf[n * 3 + m] = num(mat.arr.at(m).arr.at(n)); d.xform_end_nerf[n * 3 + m] = num(mat_end.arr.at(m).arr.at(n)); }
@@ -185,6 +193,14 @@ NerfDataset::NerfDataset(const std::vector<std::string>& json_paths) {
     }
     // scale / offset of a later json apply to every frame in the reference too (conversion runs after all jsons are read)
     for (DatasetFrame& d : frames) { nerf_matrix_to_ngp(d.xform_nerf, d.xform); nerf_matrix_to_ngp(d.xform_end_nerf, d.xform_end); }
+}
+
+void NerfDataset::set_depth(size_t i, const uint16_t* pixels, int w, int h) {
+    NGP_CHECK(i < frames.size(), "Invalid frame index");
+    DatasetFrame& d = frames[i];
+    NGP_CHECK(pixels, "Could not load depth image '" + d.depth_path + "'.");
+    if (w != d.res[0] || h != d.res[1]) throw Error("Depth image " + d.depth_path + " has wrong resolution.");
+    d.depth_pixels.assign(pixels, pixels + (size_t)w * h);
 }
 
 void NerfDataset::set_image(size_t i, const void* pixels, int data_type, int w, int h) {

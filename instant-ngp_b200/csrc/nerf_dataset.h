@@ -25,6 +25,11 @@ struct DatasetFrame {
     std::vector<uint8_t> pixels;  // converted copy (white/black-transparent rules of convert_rgba32, nerf_loader.cu:49-71)
     size_t json_index = 0, frame_index = 0;   // which json / which frame of it (after sorting and culling)
     bool white_transparent = false, black_transparent = false;   // the scene flags as they stood when this frame's json was read (LoadedImageInfo defaults)
+    // depth supervision (nerf_loader.cu:471-473,609-621): "integer_depth_scale" as it stood when this frame's json was read (-1: none), the frame's
+    // resolved "depth_path" (empty: no file to read) and its 16-bit pixels once the caller has decoded them
+    float depth_scale = -1.f;
+    std::string depth_path;
+    std::vector<uint16_t> depth_pixels;
 };
 
 class NerfDataset {
@@ -35,6 +40,8 @@ public:
     // decoded pixels of frame i: [h][w][4] uint8 (sRGB, straight alpha) or float32; focal length is resolved here because the
     // fov forms need the resolution (read_focal_length, nerf_loader.cu:229-258)
     void set_image(size_t i, const void* pixels, int data_type, int w, int h);
+    // decoded depth map of frame i: [h][w] uint16, same resolution as the image (set_image first)
+    void set_depth(size_t i, const uint16_t* pixels, int w, int h);
     bool complete() const;
 
     std::vector<DatasetFrame> frames;

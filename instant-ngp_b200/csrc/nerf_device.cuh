@@ -38,6 +38,7 @@ struct ImageMeta {
     float xform[12];            // TrainingXForm::start (mat4x3, column major)
     float xform_end[12];        // TrainingXForm::end; equal to xform unless the data set gives transform_matrix_start / _end
     float rolling_shutter[4];   // TrainingImageMetadata::rolling_shutter (nerf_loader.h:44): pixel time = A + B u + C v + D motionblur_time
+    const float* depth;         // TrainingImageMetadata::depth (nerf_loader.h:37): per-pixel depth in scene units along the view axis, or nullptr
 };
 
 // ---- stepping (what testbed_nerf.cu:124-184 computes; evaluated through struct Cone below) ----
@@ -348,6 +349,12 @@ NGP_D void read_rgba(const ImageMeta& im, float u, float v, float* rgba) {
         float4 p = __ldg(reinterpret_cast<const float4*>(im.pixels) + idx);
         rgba[0] = p.x; rgba[1] = p.y; rgba[2] = p.z; rgba[3] = p.w;
     }
+}
+
+// read_depth (common_device.cuh:927-933): the depth map at the pixel that holds uv
+NGP_D float read_depth(const ImageMeta& im, float u, float v) {
+    const int px = clampi((int)(u * (float)im.res[0]), 0, im.res[0] - 1), py = clampi((int)(v * (float)im.res[1]), 0, im.res[1] - 1);
+    return __ldg(im.depth + (size_t)px + (size_t)py * im.res[0]);
 }
 
 // ---- Owen-scrambled Sobol (random_val.cuh:151-291; Burley 2019) ----

@@ -939,7 +939,14 @@ NGP_D void load_out4(const __half* p, float* o) {
     o[0] = __half2float(h[0]); o[1] = __half2float(h[1]); o[2] = __half2float(h[2]); o[3] = __half2float(h[3]);
 }
 
-__global__ void __launch_bounds__(SCAN_BLOCK) loss_forward_kernel(uint32_t n_rays, Pcg32 rng, LossConfig cfg, uint32_t n_images, const ImageMeta* __restrict__ metas,
+// target depth of the ray's pixel along the (unnormalised) ray, loss of the composited depth against it, times lambda (:1848-1856); 0 without a map
+NGP_D float depth_loss_gradient(const LossConfig& cfg, const ImageMeta& m, const float* uv, V3 d_unnormalised, float depth_ray) {
+    const float target_depth = length3(d_unnormalised) * (m.depth ? read_depth(m, uv[0], uv[1]) : -1.0f);
+    const LG lg = loss_and_gradient(v3(target_depth, target_depth, target_depth), v3(depth_ray, depth_ray, depth_ray), cfg.depth_loss_type);
+    return target_depth > 0.0f ? cfg.depth_supervision_lambda * lg.grad.x : 0.0f;
+}
+
+__global__ void __launch_bounds__(SCAN_BLOCK) loss_forward_kernel(uint32_t n_rays, Aabb aabb, Pcg32 rng, LossConfig cfg, uint32_t n_images, const ImageMeta* __restrict__ metas,
                                                                   uint32_t ray_offset, uint32_t n_rays_global, SamplerBuffers sb, LossBuffers lb) {
     const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x;
     uint32_t cn = 0;
@@ -949,6 +956,9 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_forward_kernel(uint32_t n_ray
         const __half* no = lb.network_output + (size_t)base * 4;
         float T = 1.f; const float epsilon = 1e-4f;
         V3 rgb_ray = v3(0, 0, 0);
+        const bool with_depth = cfg.depth_supervision_lambda > 0.0f;
+        float depth_ray = 0.f;
+        const V3 ray_o = ld3(sb.rays + (size_t)i * 6);
         for (; cn < numsteps; ++cn) {
             if (T < epsilon) break;
             float o[4]; load_out4(no + (size_t)cn * 4, o);
@@ -958,6 +968,10 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_forward_kernel(uint32_t n_ray
             const float alpha = alpha_from_density(density, dt);
             const float weight = alpha * T;
             rgb_ray = rgb_ray + weight * rgb;
+            if (with_depth) {   // :1743,1752
+                const V3 pos = unwarp_position(v3(__ldg(cin + (size_t)cn * 7), __ldg(cin + (size_t)cn * 7 + 1), __ldg(cin + (size_t)cn * 7 + 2)), aabb);
+                depth_ray += weight * length3(pos - ray_o);
+            }
             T *= (1.f - alpha);
         }
         // replay the sampler's RNG stream to recover pixel + background colour (:1757-1780)
@@ -989,8 +1003,9 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_forward_kernel(uint32_t n_ray
             } else target = bg;
         }
         if (cn == numsteps) rgb_ray = rgb_ray + T * bg;
-        float* rs = lb.ray_scratch + (size_t)i * 8;
+        float* rs = lb.ray_scratch + (size_t)i * RAY_SCRATCH;
         rs[0] = rgb_ray.x; rs[1] = rgb_ray.y; rs[2] = rgb_ray.z; rs[3] = target.x; rs[4] = target.y; rs[5] = target.z; rs[6] = __uint_as_float(img); rs[7] = max_level;
+        if (with_depth) { rs[8] = depth_ray; rs[9] = depth_loss_gradient(cfg, m, uv, ld3(sb.rays + (size_t)i * 6 + 3), depth_ray); }
         lb.compacted_numsteps[i] = cn;
     }
     uint32_t total;
@@ -1012,7 +1027,7 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_backward_kernel(uint32_t n_ra
     if (cn == 0) return;
     const float* cin = sb.coords + (size_t)base * 7;
     const __half* no = lb.network_output + (size_t)base * 4;
-    const float* rs = lb.ray_scratch + (size_t)i * 8;
+    const float* rs = lb.ray_scratch + (size_t)i * RAY_SCRATCH;
     const V3 rgb_ray = ld3(rs), target = ld3(rs + 3);
     const V3 ray_o = ld3(sb.rays + (size_t)i * 6);
 
@@ -1024,6 +1039,8 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_backward_kernel(uint32_t n_ra
     const float output_l1_reg_density = *mean_density < NERF_MIN_OPTICAL_THICKNESS ? 1e-4f : 0.0f;
 
     V3 rgb_ray2 = v3(0, 0, 0); float T = 1.f;
+    const bool with_depth = cfg.depth_supervision_lambda > 0.0f;
+    const float depth_ray = with_depth ? rs[8] : 0.f, depth_gradient = with_depth ? rs[9] : 0.f; float depth_ray2 = 0.f;
     __half* gout = lb.dloss_doutput + (size_t)cbase * 4;
     float* cout = lb.coords_compacted + (size_t)cbase * 7;
     for (uint32_t j = 0; j < cn; ++j) {
@@ -1049,7 +1066,9 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_backward_kernel(uint32_t n_ra
         const float g2 = loss_scale * (dl_drgb.z * network_to_rgb_derivative(o[2], cfg.rgb_activation) + fmaxf(0.0f, output_l2_reg * o[2]));
         const float dd = network_to_density_derivative(o[3], cfg.density_activation);
         const V3 tr = T * rgb - suffix;
-        const float dl_dmlp = dd * (dt * (lg.grad.x * tr.x + lg.grad.y * tr.y + lg.grad.z * tr.z));
+        float chain = lg.grad.x * tr.x + lg.grad.y * tr.y + lg.grad.z * tr.z;
+        if (with_depth) { depth_ray2 += weight * depth; chain += depth_gradient * (T * depth - (depth_ray - depth_ray2)); }   // :1926,1934-1939
+        const float dl_dmlp = dd * (dt * chain);
         const float g3 = loss_scale * dl_dmlp + (o[3] < 0.0f ? -output_l1_reg_density : 0.0f) + (o[3] > -10.0f && depth < cfg.near_distance ? 1e-4f : 0.0f);
         __half2 h[2] = {__floats2half2_rn(g0, g1), __floats2half2_rn(g2, g3)};
         *reinterpret_cast<uint2*>(gout + (size_t)j * 4) = *reinterpret_cast<uint2*>(h);
@@ -1083,7 +1102,7 @@ NGP_D float group_inclusive_scan(float v, uint32_t lane, uint32_t gmask) {
 NGP_D float pick3(float x, float y, float z, uint32_t c) { return c == 0 ? x : (c == 1 ? y : z); }   // (declared above)
 
 template <uint32_t G>
-__global__ void __launch_bounds__(SCAN_BLOCK) loss_forward_group_kernel(uint32_t n_rays, Pcg32 rng, LossConfig cfg, uint32_t n_images, const ImageMeta* __restrict__ metas,
+__global__ void __launch_bounds__(SCAN_BLOCK) loss_forward_group_kernel(uint32_t n_rays, Aabb aabb, Pcg32 rng, LossConfig cfg, uint32_t n_images, const ImageMeta* __restrict__ metas,
                                                                         uint32_t ray_offset, uint32_t n_rays_global, SamplerBuffers sb, LossBuffers lb) {
     constexpr uint32_t RPB = SCAN_BLOCK / G;
     const uint32_t lane = threadIdx.x % G, gshift = (threadIdx.x & 31u) / G * G;
@@ -1097,6 +1116,9 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_forward_group_kernel(uint32_t
         float* tb_out = lb.t_before + base;
         float T = 1.f; const float epsilon = 1e-4f;
         V3 acc = v3(0, 0, 0);
+        const bool with_depth = cfg.depth_supervision_lambda > 0.0f;
+        float depth_acc = 0.f;
+        const V3 ray_o = ld3(sb.rays + (size_t)i * 6);
         bool stop = false;
         // software pipeline: the raw loads of chunk c+1 are in flight while the chain of chunk c is replayed
         uint2 raw_next = make_uint2(0u, 0u); float dtw_next = 0.f;
@@ -1128,9 +1150,14 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_forward_group_kernel(uint32_t
                 const float weight = alpha * Tb;
                 acc = acc + weight * rgb;
                 tb_out[idx] = Tb;
+                if (with_depth) {
+                    const V3 pos = unwarp_position(v3(__ldg(cin + (size_t)idx * 7), __ldg(cin + (size_t)idx * 7 + 1), __ldg(cin + (size_t)idx * 7 + 2)), aabb);
+                    depth_acc += weight * length3(pos - ray_o);
+                }
             }
         }
         V3 rgb_ray = v3(group_sum<G>(acc.x, gmask), group_sum<G>(acc.y, gmask), group_sum<G>(acc.z, gmask));
+        const float depth_ray = with_depth ? group_sum<G>(depth_acc, gmask) : 0.f;
         // replay the sampler's RNG stream to recover pixel + background colour (:1757-1780); uniform across the group
         const uint32_t ig = ray_offset + sb.ray_indices[i];
         rng.advance((int64_t)((uint64_t)ig * N_MAX_RANDOM_SAMPLES_PER_RAY));
@@ -1156,9 +1183,12 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_forward_group_kernel(uint32_t
             }
             float ray_c = pick3(rgb_ray.x, rgb_ray.y, rgb_ray.z, lane);
             if (cn == numsteps) ray_c = ray_c + T * bg;
-            float* rs = lb.ray_scratch + (size_t)i * 8;
+            float* rs = lb.ray_scratch + (size_t)i * RAY_SCRATCH;
             rs[lane] = ray_c; rs[3 + lane] = target;
-            if (lane == 0) { rs[6] = __uint_as_float(img); rs[7] = max_level; }
+            if (lane == 0) {
+                rs[6] = __uint_as_float(img); rs[7] = max_level;
+                if (with_depth) { rs[8] = depth_ray; rs[9] = depth_loss_gradient(cfg, m, uv, ld3(sb.rays + (size_t)i * 6 + 3), depth_ray); }
+            }
         }
         if (lane == 0) lb.compacted_numsteps[i] = cn;
     }
@@ -1187,7 +1217,7 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_backward_group_kernel(uint32_
     const float* cin = sb.coords + (size_t)base * 7;
     const __half* no = lb.network_output + (size_t)base * 4;
     const float* tb_in = lb.t_before + base;
-    const float* rs = lb.ray_scratch + (size_t)i * 8;
+    const float* rs = lb.ray_scratch + (size_t)i * RAY_SCRATCH;
     const V3 rgb_ray = ld3(rs), target = ld3(rs + 3);
     const V3 ray_o = ld3(sb.rays + (size_t)i * 6);
 
@@ -1199,6 +1229,8 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_backward_group_kernel(uint32_
     const float output_l1_reg_density = *mean_density < NERF_MIN_OPTICAL_THICKNESS ? 1e-4f : 0.0f;
 
     V3 carry = v3(0, 0, 0);   // colour composited by the chunks before this one
+    const bool with_depth = cfg.depth_supervision_lambda > 0.0f;
+    const float depth_ray = with_depth ? rs[8] : 0.f, depth_gradient = with_depth ? rs[9] : 0.f; float depth_carry = 0.f;
     __half* gout = lb.dloss_doutput + (size_t)cbase * 4;
     float* cout = lb.coords_compacted + (size_t)cbase * 7;
     for (uint32_t c0 = 0; c0 < cn; c0 += G) {
@@ -1225,6 +1257,11 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_backward_group_kernel(uint32_
         const V3 wr = weight * rgb;                                        // 0 on lanes past the end
         const V3 r2 = carry + v3(group_inclusive_scan<G>(wr.x, lane, gmask), group_inclusive_scan<G>(wr.y, lane, gmask), group_inclusive_scan<G>(wr.z, lane, gmask));
         carry = v3(__shfl_sync(gmask, r2.x, gshift + G - 1), __shfl_sync(gmask, r2.y, gshift + G - 1), __shfl_sync(gmask, r2.z, gshift + G - 1));
+        float depth_ray2 = 0.f;
+        if (with_depth) {   // uniform across the group
+            depth_ray2 = depth_carry + group_inclusive_scan<G>(weight * depth, lane, gmask);
+            depth_carry = __shfl_sync(gmask, depth_ray2, gshift + G - 1);
+        }
         if (valid) {
             const V3 suffix = rgb_ray - r2;
             const V3 dl_drgb = weight * lg.grad;
@@ -1233,7 +1270,9 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_backward_group_kernel(uint32_
             const float g2 = loss_scale * (dl_drgb.z * network_to_rgb_derivative(o[2], cfg.rgb_activation) + fmaxf(0.0f, output_l2_reg * o[2]));
             const float dd = network_to_density_derivative(o[3], cfg.density_activation);
             const V3 tr = T_after * rgb - suffix;
-            const float dl_dmlp = dd * (dt * (lg.grad.x * tr.x + lg.grad.y * tr.y + lg.grad.z * tr.z));
+            float chain = lg.grad.x * tr.x + lg.grad.y * tr.y + lg.grad.z * tr.z;
+            if (with_depth) chain += depth_gradient * (T_after * depth - (depth_ray - depth_ray2));
+            const float dl_dmlp = dd * (dt * chain);
             const float g3 = loss_scale * dl_dmlp + (o[3] < 0.0f ? -output_l1_reg_density : 0.0f) + (o[3] > -10.0f && depth < cfg.near_distance ? 1e-4f : 0.0f);
             __half2 h[2] = {__floats2half2_rn(g0, g1), __floats2half2_rn(g2, g3)};
             *reinterpret_cast<uint2*>(gout + (size_t)j * 4) = *reinterpret_cast<uint2*>(h);
@@ -1291,9 +1330,9 @@ void nerf_compute_loss(cudaStream_t s, uint32_t n_rays, Aabb aabb, uint32_t n_ra
     uint32_t G = sb.lanes_per_ray == 1 ? 1u : (n_rays <= 65536 ? 32u : 8u);
     if (const char* e = getenv("NGP_LOSS_LANES")) G = (uint32_t)atoi(e);
     const uint32_t blocks = div_round_up(n_rays, SCAN_BLOCK / G);
-    if (G == 32) loss_forward_group_kernel<32><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, rng, cfg, n_images, metas, ray_offset, n_rays_global, sb, lb);
-    else if (G == 8) loss_forward_group_kernel<8><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, rng, cfg, n_images, metas, ray_offset, n_rays_global, sb, lb);
-    else loss_forward_kernel<<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, rng, cfg, n_images, metas, ray_offset, n_rays_global, sb, lb);
+    if (G == 32) loss_forward_group_kernel<32><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, rng, cfg, n_images, metas, ray_offset, n_rays_global, sb, lb);
+    else if (G == 8) loss_forward_group_kernel<8><<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, rng, cfg, n_images, metas, ray_offset, n_rays_global, sb, lb);
+    else loss_forward_kernel<<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, rng, cfg, n_images, metas, ray_offset, n_rays_global, sb, lb);
     NGP_POST_LAUNCH();
     scan_block_totals_kernel<<<1, 1024, 0, s>>>(blocks, sb.block_steps, nullptr, &sb.counters[2], nullptr, false);
     NGP_POST_LAUNCH();

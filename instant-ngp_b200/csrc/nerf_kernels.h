@@ -78,14 +78,17 @@ struct LossConfig {
     int color_space;                // Testbed::m_color_space: 0 Linear (default) / 1 SRGB selects the target formula (testbed_nerf.cu:1801-1818)
     const float* exposure;          // [n_images][3] per-image exposure in stops (cam_exposure_gpu) or nullptr = all zero (scale exactly 1)
     float* exposure_gradient;       // [n_images][3] accumulated dL/d exposure (optimize_exposure, :1969-1983) or nullptr
+    float depth_supervision_lambda; // > 0: rays of views with a depth map add lambda * dL_depth/d(depth of the ray) to the density gradient (:1848-1856,1934-1939)
+    int depth_loss_type;            // loss of the depth term (ELossType, L1 by default)
     int max_level_rand;             // max_level_rand_training (:1775): one more draw in the replayed rng stream, the value goes to max_level_compacted
 };
+constexpr uint32_t RAY_SCRATCH = 12;
 struct LossBuffers {
     const __half* network_output;   // [*][4]
     __half* dloss_doutput;          // [max_compacted][4]
     float* coords_compacted;        // [max_compacted][7]
     float* loss;                    // [n_rays]
-    float* ray_scratch;             // [n_rays][8]: rgb_ray(3), target(3), spare
+    float* ray_scratch;             // [n_rays][RAY_SCRATCH]: rgb_ray(3), target(3), image index, level cut-off, depth of the ray, depth-loss gradient
     uint32_t* compacted_numsteps;   // [n_rays] pass-1 compacted step counts
     float* t_before;                // [max_samples] transmittance in front of each sample that survives (pass 1 -> pass 2)
     // optional: encoder outputs of the un-compacted samples (blk8, enc_width columns) are carried along with the samples that

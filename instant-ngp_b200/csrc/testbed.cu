@@ -54,6 +54,7 @@ Testbed::~Testbed() {
     m_comm.reset();
     if (m_host_counters) cudaFreeHost(m_host_counters);
     for (void* p : m_image_buffers) cudaFree(p);
+    for (float* p : m_depth_buffers) if (p) cudaFree(p);
 }
 
 static std::string read_text_file(const std::string& path, const char* what) {
@@ -176,6 +177,8 @@ void Testbed::set_nerf_dataset(cudaStream_t s, uint32_t n_images, const HostImag
     m_prefetch_valid = false; m_early_prefetch = false; m_walk_ahead_valid = false; ++m_dataset_version; m_all_images_u8 = true;
     for (void* p : m_image_buffers) cudaFree(p);
     m_image_buffers.clear(); m_image_bytes.clear();
+    for (float* p : m_depth_buffers) if (p) cudaFree(p);
+    m_depth_buffers.assign(n_images, nullptr);
     m_frame_has_mask.assign(n_images, false);
     std::vector<ImageMeta> metas(n_images);
     for (uint32_t i = 0; i < n_images; ++i) {
@@ -256,6 +259,31 @@ void Testbed::set_camera_intrinsics(cudaStream_t s, int frame_idx, float fx, flo
     m.lens_mode = LENS_PERSPECTIVE; m.lens_params[0] = m.lens_params[1] = m.lens_params[2] = m.lens_params[3] = 0.f;
     if (k1 != 0.f || k2 != 0.f || p1 != 0.f || p2 != 0.f) { m.lens_mode = LENS_OPENCV; m.lens_params[0] = k1; m.lens_params[1] = k2; m.lens_params[2] = p1; m.lens_params[3] = p2; }
     m.principal_point[0] = cx; m.principal_point[1] = cy; m.focal_length[0] = fx; m.focal_length[1] = fy;
+    upload_view_metadata(s, (uint32_t)frame_idx);
+}
+
+void Testbed::set_training_depth(cudaStream_t s, int frame_idx, const void* depth_host, int depth_type, float depth_scale) {
+    NGP_CHECK(m_mode == MODE_TB_NERF, "set_training_depth: testbed is not in Nerf mode");
+    NGP_CHECK(frame_idx >= 0 && frame_idx < (int)m_n_images, "Invalid frame index");
+    NGP_CHECK(depth_type == 0 || depth_type == 1, "set_training_depth: depth type must be uint16 (0) or float32 (1)");
+    if (m_aux_stream) NGP_CUDA_CHECK(cudaStreamSynchronize(m_aux_stream));
+    NGP_CUDA_CHECK(cudaStreamSynchronize(s));                                    // no loss kernel is reading the old map
+    ImageMeta& m = m_host_metas[frame_idx];
+    const size_t n = (size_t)m.res[0] * m.res[1];
+    if (depth_scale < 0.f) {                                                     // nerf_loader.cu:957-959: depthmemory[frame_idx].free_memory()
+        if (m_depth_buffers[frame_idx]) cudaFree(m_depth_buffers[frame_idx]);
+        m_depth_buffers[frame_idx] = nullptr; m.depth = nullptr;
+    } else {
+        if (!m_depth_buffers[frame_idx]) NGP_CUDA_CHECK(cudaMalloc(&m_depth_buffers[frame_idx], n * sizeof(float)));
+        std::vector<float> host(n, 0.f);                                         // copy_depth (nerf_loader.cu:80-90): zeros without data or with scale <= 0
+        if (depth_host && depth_scale > 0.f) {
+            if (depth_type == 0) { const uint16_t* p = (const uint16_t*)depth_host; for (size_t i = 0; i < n; ++i) host[i] = (float)p[i] * depth_scale; }
+            else { const float* p = (const float*)depth_host; for (size_t i = 0; i < n; ++i) host[i] = p[i] * depth_scale; }
+        }
+        NGP_CUDA_CHECK(cudaMemcpyAsync(m_depth_buffers[frame_idx], host.data(), n * sizeof(float), cudaMemcpyHostToDevice, s));
+        NGP_CUDA_CHECK(cudaStreamSynchronize(s));
+        m.depth = m_depth_buffers[frame_idx];
+    }
     upload_view_metadata(s, (uint32_t)frame_idx);
 }
 
@@ -680,7 +708,7 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
     __half* mlp_out = m_mlp_out.get<__half>((size_t)max_samples * 4);
     lb.network_output = mlp_out; lb.dloss_doutput = m_dloss.get<__half>((size_t)target * 4);
     lb.coords_compacted = m_coords_compacted.get<float>((size_t)target * 7); lb.loss = m_loss.get<float>(max_rays);
-    lb.ray_scratch = m_ray_scratch.get<float>((size_t)max_rays * 8); lb.compacted_numsteps = m_compacted_numsteps.get<uint32_t>(max_rays);
+    lb.ray_scratch = m_ray_scratch.get<float>((size_t)max_rays * RAY_SCRATCH); lb.compacted_numsteps = m_compacted_numsteps.get<uint32_t>(max_rays);
     m_loss_sum.get<float>(4);
     lb.t_before = m_t_before.get<float>(max_samples);
     lb.enc_width = m_nerf_net->dims.pos_width; lb.enc_out = m_nerf_net->training_encoding(target);
@@ -716,6 +744,7 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
     memcpy(lc.background_color, background_color, sizeof(lc.background_color));
     lc.loss_scale = LOSS_SCALE; lc.near_distance = near_distance; lc.color_space = color_space;
     lc.max_level_rand = max_level_rand_training; lb.max_level_compacted = max_level_compacted;
+    lc.depth_supervision_lambda = depth_supervision_lambda; lc.depth_loss_type = depth_loss_type;
     if (optimize_exposure) ensure_cam_exposure(s);
     if (m_cam_exposure_n == m_n_images && m_n_images) {   // trained (now or earlier): the targets carry the per-image exposure; gradients only while it is being optimised
         lc.exposure = m_cam_exposure.as<float>();

@@ -38,6 +38,12 @@ public:
     // Testbed::m_max_level_rand_training (testbed.h:573, python_api.cu:498): every training ray draws a level cut-off 2u, u uniform in [0,1): its samples
     // are encoded with the hash-grid levels below cut-off * n_levels only (half of the rays keep every level)
     bool max_level_rand_training = false;
+    // nerf.training.depth_supervision_lambda / depth_loss_type (testbed.h:726,699; python_api.cu:616,635): weight and loss of the depth term that views
+    // with a depth map add to the density gradient (testbed_nerf.cu:1848-1856,1934-1939)
+    float depth_supervision_lambda = 0.f; int depth_loss_type = LOSS_L1;
+    // NerfDataset::set_training_image's depth half (nerf_loader.cu:943-959): host depth map of view frame_idx (depth_type 0: uint16, 1: float32), stored
+    // as value * depth_scale; depth_scale <= 0 or a null pointer: a map of zeros ("no depth for this image"); depth_scale < 0 AND null: the map is dropped
+    void set_training_depth(cudaStream_t s, int frame_idx, const void* depth_host, int depth_type, float depth_scale);
     std::string root_dir;                                   // Testbed::m_root_dir (testbed.h:978): where configs/<mode>/ is looked for
     std::string network_config_path = "base.json";          // Testbed::m_network_config_path (testbed.h:1004)
     // load_training_data equivalents with host buffers (NerfDataset: nerf_loader.h:110-171; load_nerf_post testbed_nerf.cu:3046-3112)
@@ -199,6 +205,7 @@ private:
     float m_density_grid_mean = 0.f;      // host copy, refreshed with the loss every 16th step
     std::vector<bool> m_frame_has_mask;   // RGBA8 view contains the mask colour 0x00FF00FF (see set_training_image)
     uint32_t m_n_images = 0; int m_aabb_scale = 1; uint32_t m_max_cascade = 0;
+    std::vector<float*> m_depth_buffers;                    // per view: device depth map (NerfDataset::depthmemory) or nullptr
     std::vector<void*> m_image_buffers; std::vector<size_t> m_image_bytes; DeviceBuffer m_metas; std::vector<ImageMeta> m_host_metas;
     DeviceBuffer m_density_grid, m_density_grid_tmp, m_bitfield, m_mean, m_partials, m_grid_pos, m_grid_idx, m_grid_out;
     uint32_t m_density_grid_ema_step = 0; bool m_grid_allocated = false;

@@ -176,7 +176,7 @@ _BOOL_OPTS = {"random_bg_color", "linear_colors", "snap_to_pixel_centers", "trai
               "image_snap_to_pixel_centers", "image_linear_colors", "image_stratified", "prefetch_rays", "dp_sharded_optimizer", "device_control_law",
               "render_ground_truth", "render_with_lens_distortion", "walk_ahead", "optimize_exposure", "max_level_rand_training"}
 _FLOAT_OPTS = {"near_distance", "density_grid_decay", "render_min_transmittance", "cone_angle_constant", "exposure", "zoom", "fov", "ground_truth_alpha",
-               "render_near_distance", "exposure_l2_reg"}
+               "render_near_distance", "exposure_l2_reg", "depth_supervision_lambda"}
 _INT_OPTS = {"loss_type", "rgb_activation", "density_activation", "seed", "sampler_lanes_per_ray", "prefetch_hits", "fov_axis", "walk_ahead_hits", "walk_ahead_misses", "n_steps_between_cam_updates"}
 # enum-valued members (python_api.cu:470,522-523,686): reads come back as the enum
 _ENUM_OPTS = {}     # filled below the enum definitions
@@ -237,7 +237,7 @@ class RandomMode(enum.IntEnum):       # python_api.cu:299-305
     Stratified = 3
 
 
-_ENUM_OPTS.update({"render_mode": RenderMode, "color_space": ColorSpace, "tonemap_curve": TonemapCurve, "image_random_mode": RandomMode})
+_ENUM_OPTS.update({"depth_loss_type": LossType, "render_mode": RenderMode, "color_space": ColorSpace, "tonemap_curve": TonemapCurve, "image_random_mode": RandomMode})
 
 
 class _Namespace:
@@ -306,7 +306,8 @@ class Testbed:
                                      "density_grid_decay": "density_grid_decay", "linear_colors": "linear_colors",
                                      "snap_to_pixel_centers": "train_snap_to_pixel_centers", "view": "training_view_index",
                                      "optimize_exposure": "optimize_exposure", "exposure_l2_reg": "exposure_l2_reg",
-                                     "n_steps_between_cam_updates": "n_steps_between_cam_updates"},
+                                     "n_steps_between_cam_updates": "n_steps_between_cam_updates",
+                                     "depth_supervision_lambda": "depth_supervision_lambda", "depth_loss_type": "depth_loss_type"},
                               {"set_image": self.set_training_image, "set_camera_intrinsics": self.set_camera_intrinsics,
                                "set_camera_extrinsics": self.set_camera_extrinsics,
                                "set_camera_extrinsics_rolling_shutter": self.set_camera_extrinsics_rolling_shutter, "dataset": _Dataset(self),
@@ -589,6 +590,17 @@ class Testbed:
                     img = np.concatenate([img, alpha], axis=2)
                 img = np.ascontiguousarray(img[..., [2, 1, 0, 3]])          # BGRA -> RGBA
                 check(lib().ngp_nerf_dataset_set_image(d, i, img.ctypes.data_as(C.c_void_p), int(is_float), img.shape[1], img.shape[0]))
+                check(lib().ngp_nerf_dataset_depth_path(d, i, buf, 4096))
+                if buf.value:                   # "integer_depth_scale" + "depth_path" (nerf_loader.cu:609-621): 16-bit, one channel
+                    dimg = cv2.imread(buf.value.decode(), cv2.IMREAD_UNCHANGED)
+                    if dimg is None:
+                        raise RuntimeError(f"Could not load depth image '{buf.value.decode()}'.")
+                    if dimg.ndim == 3:
+                        dimg = dimg[..., 0]
+                    if dimg.dtype == np.uint8:  # stbi_load_16 widens 8-bit files
+                        dimg = dimg.astype(np.uint16) * 257
+                    dimg = np.ascontiguousarray(dimg, np.uint16)
+                    check(lib().ngp_nerf_dataset_set_depth(d, i, dimg.ctypes.data_as(C.c_void_p), dimg.shape[1], dimg.shape[0]))
             check(lib().ngp_testbed_load_nerf_dataset(self._h, _stream(), d))
         finally:
             lib().ngp_nerf_dataset_close(d)
@@ -618,14 +630,27 @@ class Testbed:
             return self.set_image(img.astype(np.float32))
         check(lib().ngp_testbed_set_image_rgba8(self._h, _stream(), img.ctypes.data_as(C.c_void_p), img.shape[1], img.shape[0]))
 
-    def set_training_image(self, frame_idx, pixels):
-        """nerf.training.set_image(frame_idx, img) (python_api.cu:49-67): host pixels -> the device copy of one view."""
+    def set_training_image(self, frame_idx, pixels, depth_img=None, depth_scale=1.0):
+        """nerf.training.set_image(frame_idx, img, depth_img, depth_scale) (python_api.cu:49-67): host pixels -> the device copy of one view; with
+        depth_img ([h, w] float32, or uint16) also the view's depth map, kept as value * depth_scale (scene units)."""
         if isinstance(pixels, torch.Tensor):
             assert not pixels.is_cuda and pixels.is_contiguous()
             ptr = pixels.data_ptr()
         else:
             pixels = np.ascontiguousarray(pixels); ptr = pixels.ctypes.data
         check(lib().ngp_testbed_set_training_image(self._h, _stream(), int(frame_idx), C.c_void_p(ptr)))
+        if depth_img is not None:
+            self.set_training_depth(frame_idx, depth_img, depth_scale)
+
+    def set_training_depth(self, frame_idx, depth_img, depth_scale=1.0):
+        """the depth half of NerfDataset::set_training_image (nerf_loader.cu:943-959); depth_img None with depth_scale < 0 drops the view's map"""
+        if depth_img is None:
+            check(lib().ngp_testbed_set_training_depth(self._h, _stream(), int(frame_idx), None, 1, float(depth_scale)))
+            return
+        d = np.asarray(depth_img)
+        d = np.ascontiguousarray(d, np.uint16 if d.dtype == np.uint16 else np.float32)
+        check(lib().ngp_testbed_set_training_depth(self._h, _stream(), int(frame_idx), d.ctypes.data_as(C.c_void_p), 0 if d.dtype == np.uint16 else 1,
+                                                   float(depth_scale)))
 
     def set_camera_intrinsics(self, frame_idx, fx=0.0, fy=0.0, cx=-0.5, cy=-0.5, k1=0.0, k2=0.0, p1=0.0, p2=0.0):
         """nerf.training.set_camera_intrinsics (python_api.cu:583-593)"""

@@ -122,6 +122,10 @@ def load(json_path, resolutions=None):
         length = max(F(0.000001), np.abs(hi - lo).max())
         scale = F(1) / F(length)
         offset = ((hi + lo) * F(0.5)) * -scale + F(0.5)
+    # depth supervision data (nerf_loader.cu:404,420-423,471-473,609-621,711): a frame's depth file is read only when the scene gives an
+    # "integer_depth_scale" (> 0) and loading is enabled; the map is stored as pixel * integer_depth_scale * scene scale
+    enable_depth_loading = bool(j.get("enable_depth_loading", True))
+    depth_scale = F(j["integer_depth_scale"]) if "integer_depth_scale" in j else F(-1.0)
     out = []
     for i, f in enumerate(frames):
         l = {"mode": lens["mode"], "params": list(lens["params"]), "pp": list(lens["pp"]), "rolling_shutter": list(lens["rolling_shutter"])}
@@ -130,6 +134,12 @@ def load(json_path, resolutions=None):
         m_end = f.get("transform_matrix_end", m)             # nerf_loader.cu:648-649
         rec = dict(path=resolve_path(base, f["file_path"]), xform=nerf_matrix_to_ngp(m, scale, offset, from_mitsuba), pp=l["pp"], lens_mode=l["mode"],
                    lens_params=l["params"], focal=None, xform_end=nerf_matrix_to_ngp(m_end, scale, offset, from_mitsuba), rolling_shutter=l["rolling_shutter"])
+        rec["depth_path"] = ""
+        if enable_depth_loading and depth_scale > 0 and "depth_path" in f:
+            dp = resolve_path(base, f["depth_path"])
+            if os.path.exists(dp):
+                rec["depth_path"] = dp
+        rec["depth_scale"] = F(depth_scale * scale)          # < 0: the view has no depth map at all
         if resolutions is not None:
             res = resolutions[i]
             fl = read_focal_length(j, res)

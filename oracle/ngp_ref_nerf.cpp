@@ -548,6 +548,10 @@ extern "C" void ref_generate_training_samples(uint32_t n_rays, const RefAabb* aa
 // =============================================================================================
 struct LG { V3 loss, grad; };
 static inline float cs(float a, float b) { return copysignf(a, b); }
+static float read_depth(const RefImage* m, const float* uv) {   // common_device.cuh:927-933 (image_pos :841-843)
+    int px = std::min(std::max((int)(uv[0] * (float)m->res[0]), 0), m->res[0] - 1), py = std::min(std::max((int)(uv[1] * (float)m->res[1]), 0), m->res[1] - 1);
+    return m->depth[(size_t)px + (size_t)py * m->res[0]];
+}
 static LG loss_and_gradient(V3 target, V3 pred, int type) {   // :207-283,1340-1355
     V3 diff = pred - target; LG r;
     float d[3] = {diff.x, diff.y, diff.z}, p[3] = {pred.x, pred.y, pred.z}, tg[3] = {target.x, target.y, target.z}, l[3], g[3];
@@ -581,6 +585,7 @@ extern "C" void ref_compute_loss(uint32_t n_rays, const RefAabb* aabb, uint32_t 
         const uint16_t* no = net_out + (size_t)basei * 4;
         float T = 1.f; const float epsilon = 1e-4f;
         V3 rgb_ray = v3(0, 0, 0); V3 ray_o = ld3(rays + (size_t)i * 6);
+        float depth_ray = 0.f;
         uint32_t cn = 0;
         for (; cn < numsteps; ++cn) {
             if (T < epsilon) break;
@@ -591,6 +596,7 @@ extern "C" void ref_compute_loss(uint32_t n_rays, const RefAabb* aabb, uint32_t 
             float alpha = 1.f - m_expf(-density * dt);
             float weight = alpha * T;
             rgb_ray = rgb_ray + weight * rgb;
+            depth_ray += weight * length3(unwarp_position(ld3(cin + (size_t)cn * 7), aabb) - ray_o);   // :1743,1752
             T *= (1.f - alpha);
         }
         // RNG replay (:1757-1780)
@@ -635,6 +641,12 @@ extern "C" void ref_compute_loss(uint32_t n_rays, const RefAabb* aabb, uint32_t 
         float mean_loss = (lg.loss.x + lg.loss.y + lg.loss.z) / 3.0f;
         if (out->loss) out->loss[i] = mean_loss / (float)n_global;
 
+        // depth supervision (:1848-1856): the depth map at the ray's pixel, along the unnormalised ray; views without a map give -1 = no term
+        const float target_depth = length3(ld3(rays + (size_t)i * 6 + 3)) * ((cfg->depth_supervision_lambda > 0.0f && m->depth) ? read_depth(m, uv) : -1.0f);
+        const LG lg_depth = loss_and_gradient(v3(target_depth, target_depth, target_depth), v3(depth_ray, depth_ray, depth_ray), cfg->depth_loss_type);
+        const float depth_loss_gradient = target_depth > 0.0f ? cfg->depth_supervision_lambda * lg_depth.grad.x : 0.0f;
+        float depth_ray2 = 0.f;
+
         float loss_scale = cfg->loss_scale / (float)n_global;
         const float output_l2_reg = cfg->rgb_activation == REF_ACT_EXPONENTIAL ? 1e-4f : 0.0f;
         const float output_l1_reg_density = cfg->mean_density < REF_NERF_MIN_OPTICAL_THICKNESS ? 1e-4f : 0.0f;
@@ -652,6 +664,7 @@ extern "C" void ref_compute_loss(uint32_t n_rays, const RefAabb* aabb, uint32_t 
             float alpha = 1.f - m_expf(-density * dt);
             float weight = alpha * T;
             rgb_ray2 = rgb_ray2 + weight * rgb;
+            depth_ray2 += weight * depth;
             T *= (1.f - alpha);
             V3 suffix = rgb_ray - rgb_ray2;
             V3 dl_drgb = weight * lg.grad;
@@ -660,7 +673,9 @@ extern "C" void ref_compute_loss(uint32_t n_rays, const RefAabb* aabb, uint32_t 
             float g2 = loss_scale * (dl_drgb.z * network_to_rgb_derivative(o2, cfg->rgb_activation) + fmaxf(0.0f, output_l2_reg * o2));
             float dd = network_to_density_derivative(o3, cfg->density_activation);
             V3 tr = T * rgb - suffix;
-            float dl_dmlp = dd * (dt * (lg.grad.x * tr.x + lg.grad.y * tr.y + lg.grad.z * tr.z));
+            const float depth_suffix = depth_ray - depth_ray2;
+            const float depth_supervision = depth_loss_gradient * (T * depth - depth_suffix);   // :1934-1935
+            float dl_dmlp = dd * (dt * ((lg.grad.x * tr.x + lg.grad.y * tr.y + lg.grad.z * tr.z) + depth_supervision));
             float g3 = loss_scale * dl_dmlp + (o3 < 0.0f ? -output_l1_reg_density : 0.0f) + (o3 > -10.0f && depth < cfg->near_distance ? 1e-4f : 0.0f);
             uint16_t* go = out->dloss_doutput + (size_t)(cbase + j) * 4;
             go[0] = f2h(g0); go[1] = f2h(g1); go[2] = f2h(g2); go[3] = f2h(g3);

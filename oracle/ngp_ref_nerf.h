@@ -35,6 +35,7 @@ typedef struct RefImage {
     float xform[12];           // mat4x3 column-major: x-axis, y-axis, z-axis, position (TrainingXForm::start)
     float xform_end[12];       // TrainingXForm::end (== xform unless the data set has transform_matrix_end)
     float rolling_shutter[4];  // TrainingImageMetadata::rolling_shutter (nerf_loader.h:44)
+    const float* depth;        // TrainingImageMetadata::depth (nerf_loader.h:37): [h][w] depth in scene units, or NULL
 } RefImage;
 // get_xform_given_rolling_shutter (common_device.cuh:401-408) with GLM's quat_cast / slerp / normalize / mat3_cast restated
 // (dependencies/glm/glm/gtc/quaternion.inl:47-72,81-123; ext/quaternion_common.inl:41-73; ext/quaternion_geometric.inl:11-24)
@@ -103,6 +104,8 @@ typedef struct RefLossCfg {
     int color_space;           // Testbed::m_color_space (testbed.h:907): 0 Linear (default), 1 SRGB — selects the target formula (testbed_nerf.cu:1801-1818)
     const float* exposure;     // [n_images][3] per-image exposure in stops (cam_exposure_gpu) or NULL = all zero
     float* exposure_gradient;  // [n_images][3] accumulated dL/d exposure (optimize_exposure, :1969-1983) or NULL
+    float depth_supervision_lambda;   // nerf.training.depth_supervision_lambda (0 = off; :1848-1856,1934-1939)
+    int depth_loss_type;              // nerf.training.depth_loss_type (ELossType, L1 by default: testbed.h:719)
 } RefLossCfg;
 typedef struct RefLossOut {
     uint16_t* dloss_doutput;     // [max_compacted][4] fp16

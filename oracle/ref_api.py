@@ -30,7 +30,7 @@ class AdamCfg(C.Structure):
 
 class Image(C.Structure):
     _fields_ = [("pixels", vp), ("data_type", C.c_int32), ("lens_mode", C.c_int32), ("lens_params", f32 * 4), ("res", C.c_int32 * 2),
-                ("principal_point", f32 * 2), ("focal_length", f32 * 2), ("xform", f32 * 12), ("xform_end", f32 * 12), ("rolling_shutter", f32 * 4)]
+                ("principal_point", f32 * 2), ("focal_length", f32 * 2), ("xform", f32 * 12), ("xform_end", f32 * 12), ("rolling_shutter", f32 * 4), ("depth", vp)]
 
 
 class Aabb(C.Structure):
@@ -43,7 +43,8 @@ class SamplerOut(C.Structure):
 
 class LossCfg(C.Structure):
     _fields_ = [("loss_type", i32), ("rgb_activation", i32), ("density_activation", i32), ("random_bg_color", i32), ("linear_colors", i32),
-                ("snap_to_pixel_centers", i32), ("background_color", f32 * 3), ("loss_scale", f32), ("near_distance", f32), ("mean_density", f32), ("color_space", i32), ("exposure", vp), ("exposure_gradient", vp)]
+                ("snap_to_pixel_centers", i32), ("background_color", f32 * 3), ("loss_scale", f32), ("near_distance", f32), ("mean_density", f32), ("color_space", i32), ("exposure", vp), ("exposure_gradient", vp),
+                ("depth_supervision_lambda", f32), ("depth_loss_type", i32)]
 
 
 class LossOut(C.Structure):

@@ -38,6 +38,8 @@ def _load_cpp(L, path, resolutions):
             L.check(lib.ngp_nerf_dataset_view_motion(d, i, xe.ctypes.data_as(C.c_void_p), rs.ctypes.data_as(C.c_void_p)))
             frames.append(dict(path=buf.value.decode(), xform=np.array(list(v.xform), np.float32), focal=tuple(v.focal_length), pp=tuple(v.principal_point),
                                lens_mode=v.lens_mode, lens_params=tuple(v.lens_params), res=tuple(v.res), xform_end=xe, rolling_shutter=rs))
+            L.check(lib.ngp_nerf_dataset_depth_path(d, i, buf, 4096))
+            frames[-1]["depth_path"] = buf.value.decode()
         a, s, o, m = C.c_int32(), C.c_float(), (C.c_float * 3)(), C.c_int32()
         L.check(lib.ngp_nerf_dataset_info(d, C.byref(a), C.byref(s), o, C.byref(m)))
         return dict(aabb_scale=a.value, scale=np.float32(s.value), offset=np.array(list(o), np.float32), frames=frames)
@@ -53,6 +55,7 @@ def _compare(cpp, ref, exact_focal=True):
         assert np.array_equal(a["xform_end"], b["xform_end"]) and np.array_equal(a["rolling_shutter"], np.float32(b["rolling_shutter"]))
         assert a["lens_mode"] == b["lens_mode"] and np.array_equal(np.float32(a["lens_params"]), np.float32(b["lens_params"]))
         assert np.array_equal(np.float32(a["pp"]), np.float32(b["pp"]))
+        assert a["depth_path"] == b["depth_path"]
         if exact_focal:
             assert np.array_equal(np.float32(a["focal"]), np.float32(b["focal"]))
         else:
@@ -196,3 +199,44 @@ def test_rolling_shutter_and_start_end_poses(L, tmp_path):
     assert not np.array_equal(f[1]["xform_end"], f[1]["xform"]) and np.array_equal(f[1]["rolling_shutter"], np.float32([0, 0, 1, 0]))
     assert np.array_equal(f[2]["rolling_shutter"], np.float32([0.1, 0.0, 0.5, 0.25]))
     assert np.array_equal(f[3]["xform_end"], f[3]["xform"])
+
+
+def test_depth_paths(L, tmp_path):
+    """"integer_depth_scale", "enable_depth_loading" and per-frame "depth_path" (nerf_loader.cu:404,420-423,471-473,609-621): a depth file is named
+    only for frames that have one on disk, and only when the scene carries a positive integer depth scale"""
+    import cv2
+    rng = np.random.default_rng(9)
+    frames = [{"file_path": f"f{i}", "transform_matrix": _pose(rng)} for i in range(4)]
+    (tmp_path / "depth").mkdir()
+    for i in (0, 1, 3):
+        frames[i]["depth_path"] = f"depth/d{i}.png" if i != 1 else "depth/d1"          # without extension: searched like image paths
+        if i != 3:                                                                        # frame 3 names a file that is not there
+            cv2.imwrite(str(tmp_path / "depth" / f"d{i}.png"), np.zeros((6, 8), np.uint16))
+    top = {"camera_angle_x": 0.7, "integer_depth_scale": 0.001}
+    path = _write_scene(tmp_path, top, frames)
+    cpp, ref = _load_cpp(L, path, (8, 6)), loader_ref.load(path, [(8, 6)] * 4)
+    _compare(cpp, ref, exact_focal=False)
+    got = [os.path.basename(f["depth_path"]) for f in cpp["frames"]]
+    assert got == ["d0.png", "d1.png", "", ""]
+    assert ref["frames"][0]["depth_scale"] == np.float32(np.float32(0.001) * np.float32(0.33))
+    for top2 in ({"camera_angle_x": 0.7}, {"camera_angle_x": 0.7, "integer_depth_scale": 0.001, "enable_depth_loading": False},
+                 {"camera_angle_x": 0.7, "integer_depth_scale": 0.0}):
+        path = _write_scene(tmp_path, top2, frames)
+        cpp, ref = _load_cpp(L, path, (8, 6)), loader_ref.load(path, [(8, 6)] * 4)
+        _compare(cpp, ref, exact_focal=False)
+        assert all(f["depth_path"] == "" for f in cpp["frames"])
+    # a depth map must have the resolution of its image
+    lib = L.lib()
+    d = C.c_void_p()
+    path = _write_scene(tmp_path, top, frames)
+    L.check(lib.ngp_nerf_dataset_open(os.fspath(path).encode(), C.byref(d)))
+    try:
+        px = np.zeros((6, 8, 4), np.uint8)
+        L.check(lib.ngp_nerf_dataset_set_image(d, 0, px.ctypes.data_as(C.c_void_p), 0, 8, 6))
+        bad = np.zeros((5, 8), np.uint16)
+        assert lib.ngp_nerf_dataset_set_depth(d, 0, bad.ctypes.data_as(C.c_void_p), 8, 5) != 0
+        assert "wrong resolution" in lib.ngp_last_error().decode()
+        good = np.zeros((6, 8), np.uint16)
+        L.check(lib.ngp_nerf_dataset_set_depth(d, 0, good.ctypes.data_as(C.c_void_p), 8, 6))
+    finally:
+        lib.ngp_nerf_dataset_close(d)

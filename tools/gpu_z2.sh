@@ -1,0 +1,4 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 1500 python -m pytest "tests/test_depth_gpu.py" -x -q -m gpu -k "0-301-1" > gpurun_out/z_pytest.txt 2>&1
+tail -5 gpurun_out/z_pytest.txt
