@@ -111,6 +111,11 @@ int ngp_nerf_network_inference_noalloc(ngp_nerf_network_t n, void* stream, const
 /* forward_impl + backward_impl with EGradientMode::Overwrite (:179-335): dL_dout fp16 [n][4]; grads fp16, param shaped */
 int ngp_nerf_network_forward_backward(ngp_nerf_network_t n, void* stream, const void* dev_params_fp16, const void* dev_coords, uint32_t count,
                                       const void* dev_dL_dout, void* dev_grads_fp16);
+/* the same with NerfNetwork::backward's dL_dinput (nerf_network.h:262,282-330; what train_nerf_step asks for when cameras are being optimised,
+ * testbed_nerf.cu:4071-4078): dev_dL_dcoords fp32 [n][7] receives the gradient w.r.t. the warped position (cols 0..2, through the hash grid) and
+ * the warped direction (cols 4..6, through the spherical harmonics); col 3 (dt) is not a network input and is not written */
+int ngp_nerf_network_forward_backward_input(ngp_nerf_network_t n, void* stream, const void* dev_params_fp16, const void* dev_coords, uint32_t count,
+                                            const void* dev_dL_dout, void* dev_grads_fp16, void* dev_dL_dcoords);
 
 /* ------------------------------------------------------------------------------------------------------------
  * NetworkWithInputEncoding — replaces tcnn::NetworkWithInputEncoding<T> (src/testbed.cu:4101-4113; image/SDF modes)

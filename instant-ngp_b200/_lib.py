@@ -81,6 +81,7 @@ SYMBOLS = {
     "ngp_noalloc_max_samples": (u32, []),
     "ngp_nerf_network_density": (i32, [vp, vp, vp, vp, u32, u32, vp]),
     "ngp_nerf_network_forward_backward": (i32, [vp, vp, vp, vp, u32, vp, vp]),
+    "ngp_nerf_network_forward_backward_input": (i32, [vp, vp, vp, vp, u32, vp, vp, vp]),
     "ngp_encoded_mlp_create": (i32, [cp, u32, u32, C.POINTER(vp)]),
     "ngp_encoded_mlp_destroy": (None, [vp]),
     "ngp_encoded_mlp_n_params": (u64, [vp]),

@@ -162,6 +162,12 @@ int ngp_nerf_network_forward_backward(ngp_nerf_network_t n, void* stream, const 
     n->net.forward_backward(S(stream), H(params), F(coords), count, H(dL), H(grads));
     NGP_API_END
 }
+int ngp_nerf_network_forward_backward_input(ngp_nerf_network_t n, void* stream, const void* params, const void* coords, uint32_t count, const void* dL,
+                                            void* grads, void* dL_dcoords) {
+    NGP_API_BEGIN require_device(); NGP_CHECK(n && params && coords && dL && grads && dL_dcoords, "null argument");
+    n->net.forward_backward(S(stream), H(params), F(coords), count, H(dL), H(grads), F(dL_dcoords));
+    NGP_API_END
+}
 
 // ---- NetworkWithInputEncoding ----
 int ngp_encoded_mlp_create(const char* json, uint32_t n_in, uint32_t n_out, ngp_encoded_mlp_t* out) {

@@ -336,7 +336,7 @@ __global__ void __launch_bounds__(256) grid_backward_kernel(const GridLayout g, 
 template <uint32_t D, uint32_t F>
 __global__ void __launch_bounds__(256) grid_backward_input_kernel(const GridLayout g, const __half* __restrict__ table, const float* __restrict__ x,
                                                                   uint32_t x_stride, uint32_t n, const __half* __restrict__ dy, int dy_layout,
-                                                                  float* __restrict__ dx) {
+                                                                  float* __restrict__ dx, uint32_t dx_stride, const float* __restrict__ max_level) {
     constexpr uint32_t NC = 1u << D;
     const uint32_t row = blockIdx.x * blockDim.x + threadIdx.x;
     if (row >= n) return;
@@ -344,7 +344,9 @@ __global__ void __launch_bounds__(256) grid_backward_input_kernel(const GridLayo
     float out[D];
 #pragma unroll
     for (uint32_t d = 0; d < D; ++d) out[d] = 0.0f;
+    const float ml = max_level ? __ldg(max_level + row) * (float)g.n_levels + 1e-3f : 3.0e38f;   // levels cut off in the forward pass have dy/dx = 0
     for (uint32_t level = 0; level < g.n_levels; ++level) {
+        if ((float)level >= ml) break;
         const Cell<D> cell = locate<D>(xp, g.scales[level]);
         const __half* t = table + (size_t)g.offsets[level] * F;
         float v[NC][F];
@@ -377,7 +379,7 @@ __global__ void __launch_bounds__(256) grid_backward_input_kernel(const GridLayo
         }
     }
 #pragma unroll
-    for (uint32_t d = 0; d < D; ++d) dx[(size_t)row * D + d] = out[d];
+    for (uint32_t d = 0; d < D; ++d) dx[(size_t)row * dx_stride + d] = out[d];
 }
 
 template <uint32_t D>
@@ -456,10 +458,10 @@ void grid_backward_chunks(cudaStream_t s, const GridLayout& g, const float* x, u
 }
 
 void grid_backward_input(cudaStream_t s, const GridLayout& g, const __half* table, const float* x, uint32_t x_stride,
-                         uint32_t n, const __half* dy, int dy_layout, float* dx) {
+                         uint32_t n, const __half* dy, int dy_layout, float* dx, uint32_t dx_stride, const float* max_level) {
     if (n == 0) return;
     const uint32_t blocks = div_round_up(n, 256);
-    GRID_DISPATCH(grid_backward_input_kernel, g, table, x, x_stride, n, dy, dy_layout, dx);
+    GRID_DISPATCH(grid_backward_input_kernel, g, table, x, x_stride, n, dy, dy_layout, dx, dx_stride ? dx_stride : g.n_dims, max_level);
 }
 
 void grid_corners(cudaStream_t s, const GridLayout& g, const float* x, uint32_t x_stride, uint32_t n, uint32_t level,

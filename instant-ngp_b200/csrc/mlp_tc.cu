@@ -109,6 +109,22 @@ NGP_D void sh4(float dx, float dy, float dz, float* o) {
     o[15] = 0.59004358992664352f * x * (-x2 + 3.0f * y2);
 }
 
+// dL/d(direction input) from dL/d(SH4 outputs): the analytic derivatives of the 16 polynomials above, times 2 for x = 2 d - 1
+// (tcnn SphericalHarmonicsEncoding backward with input gradients; NerfNetwork::backward_impl, nerf_network.h:282-296)
+NGP_D void sh4_input_gradient(float dx, float dy, float dz, const float* g, float* out) {
+    const float x = dx * 2.f - 1.f, y = dy * 2.f - 1.f, z = dz * 2.f - 1.f;
+    const float xy = x * y, xz = x * z, yz = y * z, x2 = x * x, y2 = y * y, z2 = z * z;
+    const float c1 = 0.48860251190291987f, c2 = 1.0925484305920792f, c3 = 0.94617469575755997f, c4 = 0.54627421529603959f, c5 = 0.59004358992664352f,
+                c6 = 2.8906114426405538f, c7 = 0.45704579946446572f, c8 = 0.3731763325901154f, c9 = 1.4453057213202769f;
+    const float gx = -c1 * g[3] + c2 * y * g[4] - c2 * z * g[7] + 2.f * c4 * x * g[8] - 6.f * c5 * xy * g[9] + c6 * yz * g[10] + c7 * (1.f - 5.f * z2) * g[13] +
+                     2.f * c9 * xz * g[14] + c5 * (-3.f * x2 + 3.f * y2) * g[15];
+    const float gy = -c1 * g[1] + c2 * x * g[4] - c2 * z * g[5] - 2.f * c4 * y * g[8] + c5 * (-3.f * x2 + 3.f * y2) * g[9] + c6 * xz * g[10] + c7 * (1.f - 5.f * z2) * g[11] -
+                     2.f * c9 * yz * g[14] + 6.f * c5 * xy * g[15];
+    const float gz = c1 * g[2] - c2 * y * g[5] + 2.f * c3 * z * g[6] - c2 * x * g[7] + c6 * xy * g[10] - 10.f * c7 * yz * g[11] + c8 * (15.f * z2 - 3.f) * g[12] -
+                     10.f * c7 * xz * g[13] + c9 * (x2 - y2) * g[14];
+    out[0] = 2.f * gx; out[1] = 2.f * gy; out[2] = 2.f * gz;
+}
+
 // One MMA stage: make this thread's smem writes visible to the async proxy, sync the CTA, let thread 0 issue.
 // `issue` is a lambda run by thread 0 only.  All threads return once the MMAs have completed.
 struct StageSync {
@@ -435,6 +451,7 @@ struct BwdParams {
     __half* dL_denc;      // nullable
     float* wgrad;         // [n_density_params + n_rgb_params] fp32, atomically accumulated
     uint32_t n_tiles;
+    float* dL_dcoords;    // nullable, NeRF mode: [n][7] fp32 gradient of the loss w.r.t. the network input rows; this kernel writes the direction part (cols 4..6)
     unsigned long long* probe;   // debug (NGP_MLP_PROBE=1): per CTA [4] = %globaltimer at start / after the prologue / after the tile loop / at exit; null otherwise
 };
 
@@ -616,6 +633,15 @@ __global__ void __launch_bounds__(128) mlp_backward_kernel(const BwdParams p) {
                 *reinterpret_cast<uint4*>(go + blk8_chunk_offset(tid, 1, 16)) = make_uint4(0, 0, 0, 0);
             }
             bwd_chain<RH, 32, true>(stage, tmem_base, tmem_row, sbase, smem, Cfg::ACC_R0, Cfg::ACC_RH, Cfg::ACC_RO, L.r0, L.hr, L.g, L.go, L.wr, accumulate, tid);
+            if (p.dL_dcoords) {   // d(rgb input)[16:32] = dL/d(SH4(dir)), stored in network precision by the reference, -> dL/d(dir)
+                float gsh[16];
+                tmem_ld16(tmem_row + 16, gsh); tmem_wait_ld();
+#pragma unroll
+                for (int k = 0; k < 16; ++k) gsh[k] = __half2float(__float2half_rn(gsh[k]));
+                float gd[3]; sh4_input_gradient(dir[0], dir[1], dir[2], gsh, gd);
+                float* dst = p.dL_dcoords + (size_t)row_g * 7 + 4;
+                dst[0] = gd[0]; dst[1] = gd[1]; dst[2] = gd[2];
+            }
             // ---- d(density out) = d(rgb input)[0:16], + dL/dsigma on channel 0: add_density_gradient (nerf_network.h:62-74) ----
             float dd[16];
             tmem_ld16(tmem_row, dd); tmem_wait_ld();
@@ -806,10 +832,10 @@ void nerf_mlp_density(cudaStream_t s, const NerfNetDims& d, const __half* wd, co
 }
 
 void nerf_mlp_backward(cudaStream_t s, const NerfNetDims& d, const __half* wd, const __half* wr, const __half* enc, const float* coords,
-                       uint32_t n, const __half* dL_dout, __half* dL_denc, float* wgrad) {
+                       uint32_t n, const __half* dL_dout, __half* dL_denc, float* wgrad, float* dL_dcoords) {
     if (n == 0) return;
     NGP_PROFILE_SCOPE(s, "nerf_mlp_backward", n);
-    BwdParams p{wd, wr, enc, coords, dL_dout, 4, dL_denc, wgrad, tiles_of(n), nullptr};
+    BwdParams p{wd, wr, enc, coords, dL_dout, 4, dL_denc, wgrad, tiles_of(n), dL_dcoords, nullptr};
     NERF_DISPATCH(launch_bwd, MODE_NERF, d, s, p);
 }
 
@@ -826,7 +852,7 @@ void mlp_backward(cudaStream_t s, uint32_t in_w, uint32_t nh, const __half* w, c
     if (n == 0) return;
     NGP_CHECK(dout_stride % 8 == 0 && dout_stride >= 16, "mlp_backward: dout_stride must be a multiple of 8 and >= 16");
     NGP_PROFILE_SCOPE(s, "mlp_backward", n);
-    BwdParams p{w, nullptr, in, nullptr, dL_dout, dout_stride, dL_din, wgrad, tiles_of(n), nullptr};
+    BwdParams p{w, nullptr, in, nullptr, dL_dout, dout_stride, dL_din, wgrad, tiles_of(n), nullptr, nullptr};
     PLAIN_DISPATCH(launch_bwd, in_w, nh, s, p);
 }
 

@@ -103,28 +103,30 @@ void NerfNetwork::density(cudaStream_t s, const __half* params, const float* pos
     nerf_mlp_density(s, dims, params + off_density, enc, n, out);
 }
 
-void NerfNetwork::forward_backward(cudaStream_t s, const __half* params, const float* coords, uint32_t n, const __half* dL_dout, __half* grads) {
+void NerfNetwork::forward_backward(cudaStream_t s, const __half* params, const float* coords, uint32_t n, const __half* dL_dout, __half* grads, float* dL_dcoords) {
     __half* enc = enc_buf.get<__half>((size_t)n * dims.pos_width);
     __half* denc = denc_buf.get<__half>((size_t)n * dims.pos_width);
     float* wg = wgrad_buf.get<float>(n_matrix_params);
     NGP_CUDA_CHECK(cudaMemsetAsync(wg, 0, n_matrix_params * sizeof(float), s));
     NGP_CUDA_CHECK(cudaMemsetAsync(grads + off_grid, 0, grid.n_params * sizeof(__half), s));
     grid_forward(s, grid, params + off_grid, coords, 7, n, enc, LAYOUT_BLK8, nullptr, max_level_gpu);
-    nerf_mlp_backward(s, dims, params + off_density, params + off_rgb, enc, coords, n, dL_dout, denc, wg);
+    nerf_mlp_backward(s, dims, params + off_density, params + off_rgb, enc, coords, n, dL_dout, denc, wg, dL_dcoords);
     cast_f32_to_half(s, wg, grads, n_matrix_params);
     grid_backward(s, grid, coords, 7, n, denc, LAYOUT_BLK8, grads + off_grid, max_level_gpu);
+    if (dL_dcoords) grid_backward_input(s, grid, params + off_grid, coords, 7, n, denc, LAYOUT_BLK8, dL_dcoords, 7, max_level_gpu);
 }
 
 void NerfNetwork::forward_backward_encoded(cudaStream_t s, const __half* params, const float* coords, uint32_t n, const __half* dL_dout, __half* grads,
-                                           cudaEvent_t after_mlp, bool grid_grads_clean, const std::function<void(size_t, size_t)>* slice_ready) {
+                                           cudaEvent_t after_mlp, bool grid_grads_clean, const std::function<void(size_t, size_t)>* slice_ready, float* dL_dcoords) {
     const __half* enc = enc_train_buf.as<__half>();
     __half* denc = denc_buf.get<__half>((size_t)n * dims.pos_width);
     float* wg = wgrad_buf.get<float>(n_matrix_params);
     NGP_CUDA_CHECK(cudaMemsetAsync(wg, 0, n_matrix_params * sizeof(float), s));
     if (!grid_grads_clean) NGP_CUDA_CHECK(cudaMemsetAsync(grads + off_grid, 0, grid.n_params * sizeof(__half), s));
-    nerf_mlp_backward(s, dims, params + off_density, params + off_rgb, enc, coords, n, dL_dout, denc, wg);
+    nerf_mlp_backward(s, dims, params + off_density, params + off_rgb, enc, coords, n, dL_dout, denc, wg, dL_dcoords);
     cast_f32_to_half(s, wg, grads, n_matrix_params);
     if (after_mlp) NGP_CUDA_CHECK(cudaEventRecord(after_mlp, s));
+    if (dL_dcoords) grid_backward_input(s, grid, params + off_grid, coords, 7, n, denc, LAYOUT_BLK8, dL_dcoords, 7, max_level_gpu);
     if (!slice_ready) { grid_backward(s, grid, coords, 7, n, denc, LAYOUT_BLK8, grads + off_grid, max_level_gpu); return; }
     // data-parallel step: hand every finished slice of the gradient vector to the caller (who all-reduces it on another stream).
     // The hash-grid pass can be cut into `groups` launches of consecutive level chunks (NGP_DP_SLICES) so that the collective

@@ -48,11 +48,13 @@ struct NerfNetwork {
     // pos [n][pos_stride] fp32; out [n] fp16 (raw density)
     void density(cudaStream_t s, const __half* params, const float* pos, uint32_t pos_stride, uint32_t n, __half* out);
     // forward(recompute)+backward; grads: param-shaped fp16, OVERWRITTEN (EGradientMode::Overwrite, testbed_nerf.cu:4078)
-    void forward_backward(cudaStream_t s, const __half* params, const float* coords, uint32_t n, const __half* dL_dout, __half* grads);
+    // dL_dcoords (optional): [n][7] fp32, the gradient w.r.t. the input rows (NerfNetwork::backward's dL_dinput, nerf_network.h:282-330): position
+    // cols 0..2 through the hash grid, direction cols 4..6 through SH4; col 3 (dt) is not an input of the network and is left alone
+    void forward_backward(cudaStream_t s, const __half* params, const float* coords, uint32_t n, const __half* dL_dout, __half* grads, float* dL_dcoords = nullptr);
     // same, with the encoder outputs of the n samples already known (blk8 rows in enc_train_buf, carried over from inference())
     void forward_backward_encoded(cudaStream_t s, const __half* params, const float* coords, uint32_t n, const __half* dL_dout, __half* grads,
                                   cudaEvent_t after_mlp = nullptr, bool grid_grads_clean = false,
-                                  const std::function<void(size_t, size_t)>* slice_ready = nullptr);   // (offset, count) of `grads` complete on s   // recorded between the MLP and the hash-grid backward kernels
+                                  const std::function<void(size_t, size_t)>* slice_ready = nullptr, float* dL_dcoords = nullptr);   // (offset, count) of `grads` complete on s   // recorded between the MLP and the hash-grid backward kernels
     const __half* last_inference_encoding() const { return enc_buf.as<__half>(); }
     __half* training_encoding(uint32_t n) { return enc_train_buf.get<__half>((size_t)n * dims.pos_width); }
 };

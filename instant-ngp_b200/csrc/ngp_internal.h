@@ -46,7 +46,7 @@ void grid_backward_chunks(cudaStream_t s, const GridLayout& g, const float* x, u
                           int dy_layout, __half* grad, uint32_t chunk0, uint32_t n_chunks, const float* max_level = nullptr);
 // dL/dx [n][n_dims] fp32
 void grid_backward_input(cudaStream_t s, const GridLayout& g, const __half* table, const float* x, uint32_t x_stride,
-                         uint32_t n, const __half* dy, int dy_layout, float* dx);
+                         uint32_t n, const __half* dy, int dy_layout, float* dx, uint32_t dx_stride = 0, const float* max_level = nullptr);   // dx_stride 0: n_dims
 // debug / parity: level-local corner indices [n][2^D] and weights for one level
 void grid_corners(cudaStream_t s, const GridLayout& g, const float* x, uint32_t x_stride, uint32_t n, uint32_t level,
                   uint32_t* idx, float* w);
@@ -76,7 +76,8 @@ void nerf_mlp_density(cudaStream_t s, const NerfNetDims& d, const __half* w_dens
 // Forward recompute + backward on n samples.  dL_dout: [n][4] fp16.  Outputs: dL_denc [n x pos_width] blk8 fp16,
 // wgrad_f32: [n_density_params + n_rgb_params] fp32, ACCUMULATED with atomics (caller zeroes).
 void nerf_mlp_backward(cudaStream_t s, const NerfNetDims& d, const __half* w_density, const __half* w_rgb, const __half* enc,
-                       const float* coords, uint32_t n, const __half* dL_dout, __half* dL_denc, float* wgrad_f32);
+                       const float* coords, uint32_t n, const __half* dL_dout, __half* dL_denc, float* wgrad_f32, float* dL_dcoords = nullptr);
+// dL_dcoords (optional): [n][7] fp32 input gradients; the kernel writes the direction part (cols 4..6) = dL/d(SH4 encoding) x dSH4/d(dir)
 
 // Plain MLP (image / SDF mode: NetworkWithInputEncoding, testbed.cu:4110): in_w in {16,32}, n_hidden in {1,2,3}
 //   out: [n][out_stride] fp16, first 16 columns written

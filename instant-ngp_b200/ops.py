@@ -142,12 +142,17 @@ class NerfNetwork:
         check(lib().ngp_nerf_network_density(self._h, _stream(), _ptr(params), _ptr(pos), pos.shape[1], n, _ptr(out)))
         return out
 
-    def forward_backward(self, params, coords, dL_dout, grads=None):
+    def forward_backward(self, params, coords, dL_dout, grads=None, input_gradients=False):
+        """input_gradients: also return dL/d(coords) [n, 7] fp32 (position through the hash grid, direction through SH4; the dt column stays 0)"""
         _dev(params, torch.float16); _dev(coords, torch.float32); _dev(dL_dout, torch.float16)
         if grads is None:
             grads = torch.empty(self.n_params(), dtype=torch.float16, device="cuda")
-        check(lib().ngp_nerf_network_forward_backward(self._h, _stream(), _ptr(params), _ptr(coords), coords.shape[0], _ptr(dL_dout), _ptr(grads)))
-        return grads
+        if not input_gradients:
+            check(lib().ngp_nerf_network_forward_backward(self._h, _stream(), _ptr(params), _ptr(coords), coords.shape[0], _ptr(dL_dout), _ptr(grads)))
+            return grads
+        dc = torch.zeros(coords.shape[0], 7, dtype=torch.float32, device="cuda")
+        check(lib().ngp_nerf_network_forward_backward_input(self._h, _stream(), _ptr(params), _ptr(coords), coords.shape[0], _ptr(dL_dout), _ptr(grads), _ptr(dc)))
+        return grads, dc
 
 
 class NetworkWithInputEncoding:

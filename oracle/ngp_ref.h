@@ -114,6 +114,11 @@ void ref_nerf_density(const RefNerfNetCfg* c, const uint16_t* params, const floa
 // full fwd+bwd: dL_dout [n][4] fp16 -> grads (double, params-shaped, +=)
 void ref_nerf_backward(const RefNerfNetCfg* c, const uint16_t* params, const float* coords, uint32_t n,
                        const uint16_t* dL_dout, double* grads);
+// the same, also returning dL/d(coords) [n][7] fp32 (NerfNetwork::backward's dL_dinput: position cols 0..2, direction cols 4..6)
+void ref_nerf_backward_input(const RefNerfNetCfg* c, const uint16_t* params, const float* coords, uint32_t n,
+                             const uint16_t* dL_dout, double* grads, float* dL_dcoords);
+// d(SH4 output k)/d(direction input axis a), J[16][3] row-major, for one direction in [0,1]^3
+void ref_sh4_jacobian(const float* dir3, float* J48);
 void ref_nerf_init(const RefNerfNetCfg* c, uint64_t seed, float* params_fp32);
 
 // -- optimizer: Ema(ExponentialDecay(Adam)) (configs/nerf/base.json:5-22) -----------------------------

@@ -259,6 +259,34 @@ static inline void sh4_one(const float* d, float* o) {
     o[14] = 1.4453057213202769f * z * (x2 - y2);
     o[15] = 0.59004358992664352f * x * (-x2 + 3.0f * y2);
 }
+// d(SH4 outputs)/d(direction input in [0,1]^3): J[k][axis], the analytic partials of the polynomials in sh4_one times 2 (x = 2 d - 1).
+// tiny-cuda-nn's SphericalHarmonicsEncoding hands exactly these to its backward pass (dy_dx); restated from the polynomials, pinned by finite
+// differences in tests/test_oracle_cpu.py.
+static void sh4_jacobian(const float* d, float J[16][3]) {
+    const float x = d[0] * 2.f - 1.f, y = d[1] * 2.f - 1.f, z = d[2] * 2.f - 1.f;
+    const float C1 = 0.48860251190291987f, C2 = 1.0925484305920792f, C3 = 0.94617469575755997f, C4 = 0.54627421529603959f, C5 = 0.59004358992664352f,
+                C6 = 2.8906114426405538f, C7 = 0.45704579946446572f, C8 = 0.3731763325901154f, C9 = 1.4453057213202769f;
+    const float P[16][3] = {
+        {0.f, 0.f, 0.f},
+        {0.f, -C1, 0.f},
+        {0.f, 0.f, C1},
+        {-C1, 0.f, 0.f},
+        {C2 * y, C2 * x, 0.f},
+        {0.f, -C2 * z, -C2 * y},
+        {0.f, 0.f, 2.f * C3 * z},
+        {-C2 * z, 0.f, -C2 * x},
+        {2.f * C4 * x, -2.f * C4 * y, 0.f},
+        {C5 * y * (-6.f * x), C5 * (-3.f * x * x + 3.f * y * y), 0.f},
+        {C6 * y * z, C6 * x * z, C6 * x * y},
+        {0.f, C7 * (1.f - 5.f * z * z), C7 * y * (-10.f * z)},
+        {0.f, 0.f, C8 * (15.f * z * z - 3.f)},
+        {C7 * (1.f - 5.f * z * z), 0.f, C7 * x * (-10.f * z)},
+        {C9 * z * 2.f * x, C9 * z * (-2.f * y), C9 * (x * x - y * y)},
+        {C5 * (-3.f * x * x + 3.f * y * y), C5 * x * (6.f * y), 0.f}};
+    for (int k = 0; k < 16; ++k) for (int a = 0; a < 3; ++a) J[k][a] = 2.f * P[k][a];
+}
+extern "C" void ref_sh4_jacobian(const float* dir3, float* J48) { float J[16][3]; sh4_jacobian(dir3, J); memcpy(J48, J, sizeof(J)); }
+
 extern "C" void ref_sh4(const float* dirs, uint32_t stride, uint32_t n, uint16_t* out, uint32_t os) {
     for (uint32_t i = 0; i < n; ++i) {
         float o[16]; sh4_one(dirs + (size_t)i * stride, o);
@@ -425,8 +453,15 @@ extern "C" void ref_nerf_density(const RefNerfNetCfg* c, const uint16_t* params,
     }
 }
 
+static void nerf_backward_impl(const RefNerfNetCfg* c, const uint16_t* params, const float* coords, uint32_t n, const uint16_t* dL_dout, double* grads, float* dL_dcoords);
 extern "C" void ref_nerf_backward(const RefNerfNetCfg* c, const uint16_t* params, const float* coords, uint32_t n,
-                                  const uint16_t* dL_dout, double* grads) {
+                                  const uint16_t* dL_dout, double* grads) { nerf_backward_impl(c, params, coords, n, dL_dout, grads, nullptr); }
+// the same with NerfNetwork::backward's dL_dinput (nerf_network.h:262,282-330): dL_dcoords [n][7] fp32, position through the hash grid
+// (dL/d encoding in network precision), direction through SH4 (dL/d SH in network precision); the dt column is not written
+extern "C" void ref_nerf_backward_input(const RefNerfNetCfg* c, const uint16_t* params, const float* coords, uint32_t n,
+                                        const uint16_t* dL_dout, double* grads, float* dL_dcoords) { nerf_backward_impl(c, params, coords, n, dL_dout, grads, dL_dcoords); }
+static void nerf_backward_impl(const RefNerfNetCfg* c, const uint16_t* params, const float* coords, uint32_t n,
+                                  const uint16_t* dL_dout, double* grads, float* dL_dcoords) {
     uint64_t od, orr, og; ref_nerf_n_params(c, &od, &orr, &og);
     uint32_t pw = ref_nerf_pos_width(c);
     for (uint32_t s = 0; s < n; ++s) {
@@ -444,6 +479,16 @@ extern "C" void ref_nerf_backward(const RefNerfNetCfg* c, const uint16_t* params
         g_grid_max_level = g_nerf_max_level ? g_nerf_max_level + s : nullptr;
         ref_grid_backward(&c->grid, coords + (size_t)s * 7, 7, 1, dench, pw, grads + og);
         g_grid_max_level = nullptr;
+        if (dL_dcoords) {
+            float* dc = dL_dcoords + (size_t)s * 7;
+            float J[16][3]; sh4_jacobian(coords + (size_t)s * 7 + 4, J);
+            for (int a = 0; a < 3; ++a) { float acc = 0.f; for (int k = 0; k < 16; ++k) acc += rh(drin[16 + k]) * J[k][a]; dc[4 + a] = acc; }
+            if (g_nerf_max_level) {   // levels the forward pass zeroed have no input derivative either
+                const float ml = g_nerf_max_level[s] * (float)c->grid.n_levels + 1e-3f;
+                for (uint32_t l = 0; l < c->grid.n_levels; ++l) if ((float)l >= ml) for (uint32_t f = 0; f < c->grid.n_features; ++f) dench[l * c->grid.n_features + f] = 0;
+            }
+            ref_grid_backward_input(&c->grid, params + og, coords + (size_t)s * 7, 7, 1, dench, pw, dc);
+        }
     }
 }
 

@@ -218,6 +218,20 @@ def nerf_backward(cfg, params_h, coords, dL_h, max_level=None):
     return g
 
 
+def nerf_backward_input(cfg, params_h, coords, dL_h, max_level=None):
+    """-> (parameter gradients, dL/d coords [n, 7])"""
+    g = np.zeros(nerf_n_params(cfg)[0], np.float64); dc = np.zeros((coords.shape[0], 7), np.float32)
+    _with_max_level("ref_nerf_set_max_level", max_level,
+                    lambda: lib().ref_nerf_backward_input(C.byref(cfg), P(params_h), P(coords), u32(coords.shape[0]), P(dL_h), P(g), P(dc)))
+    return g, dc
+
+
+def sh4_jacobian(direction):
+    J = np.zeros((16, 3), np.float32); d = np.ascontiguousarray(direction, np.float32)
+    lib().ref_sh4_jacobian(P(d), P(J))
+    return J
+
+
 def pcg32_floats(seed, skip, n):
     out = np.zeros(n, np.float32)
     lib().ref_pcg32_fill_float(u64(seed), u64(skip), P(out), C.c_size_t(n))

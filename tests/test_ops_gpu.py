@@ -192,6 +192,32 @@ def test_nerf_network_forward_backward(ops, ref, cfg_json):
     assert ((gh != 0) == (np.abs(ghr) > 0)).mean() > 0.999
 
 
+@pytest.mark.parametrize("cfg_json", [NERF_CFG_16x2, NERF_CFG_FORK])
+def test_nerf_network_input_gradients(ops, ref, cfg_json):
+    """NerfNetwork::backward's dL_dinput (nerf_network.h:262,282-330), what the camera optimisation consumes: position through the hash grid,
+    direction through SH4; parameter gradients unchanged by asking for it"""
+    net, rcfg = _nerf(ops, ref, cfg_json)
+    rng = np.random.default_rng(23)
+    params = _random_params(net, rng)
+    n = 640
+    coords = _coords(ref, n, seed=6)
+    dL = (rng.normal(0, 1, (n, 4)) / 64).astype(np.float16)
+    g, dc = net.forward_backward(_cuda(params), _cuda(coords), _cuda(dL), input_gradients=True)
+    g0 = net.forward_backward(_cuda(params), _cuda(coords), _cuda(dL))
+    nm = net.n_matrix_params                                   # (fp32 atomics of the weight-gradient flush: equal up to summation order)
+    assert torch.allclose(g[:nm].float(), g0[:nm].float(), rtol=4e-3, atol=1e-5)
+    dc = dc.cpu().numpy()
+    gr, dcr = ref.nerf_backward_input(rcfg, params, coords, dL)
+    assert np.all(dc[:, 3] == 0) and np.all(dcr[:, 3] == 0)
+    for cols, what in ((slice(0, 3), "position"), (slice(4, 7), "direction")):
+        a, b = dc[:, cols], dcr[:, cols]
+        scale = np.abs(b).max()
+        assert scale > 0
+        # the chain ends in fp16 quantities on both sides (dL/d encoding); fp32 tensor-core sums against the oracle's sequential ones
+        assert np.abs(a - b).max() <= 2e-2 * scale, (what, np.abs(a - b).max(), scale)
+        assert np.linalg.norm(a - b) <= 1e-2 * np.linalg.norm(b), (what, np.linalg.norm(a - b), np.linalg.norm(b))
+
+
 def test_encoded_mlp_image_network(ops, ref):
     cfg_json = {"encoding": {"otype": "HashGrid", "n_levels": 16, "n_features_per_level": 2, "log2_hashmap_size": 15, "base_resolution": 16},
                 "network": {"otype": "FullyFusedMLP", "activation": "ReLU", "output_activation": "None", "n_neurons": 64, "n_hidden_layers": 2}}

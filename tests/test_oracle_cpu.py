@@ -293,3 +293,29 @@ def test_halton_known_values(ref):
     ref.lib().ref_image_positions_ld(ref.i32(1), ref.u64(0), ref.u32(0), ref.u32(9), ref.P(pos))
     np.testing.assert_allclose(pos[:, 0], [0, 1 / 2, 1 / 4, 3 / 4, 1 / 8, 5 / 8, 3 / 8, 7 / 8, 1 / 16], rtol=1e-6)
     np.testing.assert_allclose(pos[:, 1], [0, 1 / 3, 2 / 3, 1 / 9, 4 / 9, 7 / 9, 2 / 9, 5 / 9, 8 / 9], rtol=1e-6)
+
+
+def test_sh4_jacobian_matches_finite_differences(ref):
+    """d SH4 / d direction (the input gradient the camera optimisation needs): the oracle's analytic partials against central differences of a
+    float64 evaluation of the same real spherical harmonics written from their closed forms (Cartesian, unnormalised argument as tcnn uses them)"""
+    def sh(d):
+        x, y, z = (2.0 * np.asarray(d, np.float64) - 1.0)
+        return np.array([
+            0.28209479177387814, -0.48860251190291987 * y, 0.48860251190291987 * z, -0.48860251190291987 * x,
+            1.0925484305920792 * x * y, -1.0925484305920792 * y * z, 0.94617469575755997 * z * z - 0.31539156525251999, -1.0925484305920792 * x * z,
+            0.54627421529603959 * (x * x - y * y), 0.59004358992664352 * y * (y * y - 3.0 * x * x), 2.8906114426405538 * x * y * z,
+            0.45704579946446572 * y * (1.0 - 5.0 * z * z), 0.3731763325901154 * z * (5.0 * z * z - 3.0), 0.45704579946446572 * x * (1.0 - 5.0 * z * z),
+            1.4453057213202769 * z * (x * x - y * y), 0.59004358992664352 * x * (3.0 * y * y - x * x)])
+    rng = np.random.default_rng(2)
+    dirs = rng.uniform(0, 1, (64, 3)).astype(np.float32)
+    # the float64 closed forms are the encoding the oracle computes (to fp16 rounding of its output)
+    out = np.zeros((64, 16), np.float16)
+    ref.lib().ref_sh4(ref.P(dirs), C.c_uint32(3), C.c_uint32(64), ref.P(out), C.c_uint32(16))
+    want = np.stack([sh(d) for d in dirs])
+    assert np.abs(out.astype(np.float64) - want).max() <= 2e-3
+    h = 1e-5
+    for d in dirs:
+        J = ref.sh4_jacobian(d).astype(np.float64)
+        fd = np.stack([(sh(d.astype(np.float64) + h * e) - sh(d.astype(np.float64) - h * e)) / (2 * h) for e in np.eye(3)], axis=1)
+        assert np.abs(J - fd).max() <= 2e-5 * max(1.0, np.abs(fd).max()), (d, np.abs(J - fd).max())
+    assert np.all(ref.sh4_jacobian(np.float32([0.3, 0.6, 0.9]))[0] == 0)
