@@ -233,6 +233,11 @@ int ngp_testbed_set_camera_extrinsics(ngp_testbed_t t, void* stream, int32_t fra
  * position linearly, rotation by quaternion slerp).  The loader sets both from "transform_matrix_start" / "_end" and "rolling_shutter". */
 int ngp_testbed_set_camera_extrinsics_rolling_shutter(ngp_testbed_t t, void* stream, int32_t frame_idx, const float* camera_to_world_start,
                                                       const float* camera_to_world_end, const float* rolling_shutter4, int32_t convert_to_ngp);
+/* nerf.training.get_camera_extrinsics(frame_idx, convert_to_ngp = True) (python_api.cu:594-603, testbed_nerf.cu:2925-2932): the pose of view frame_idx
+ * as training sees it - the given pose with the trained rotation / position offsets of optimize_extrinsics applied - as a column-major mat4x3,
+ * converted back to the NeRF convention when convert_to_ngp is set (the flag is named as in the reference: it means "the matrix I want is in the
+ * convention I would pass WITH convert_to_ngp") */
+int ngp_testbed_get_camera_extrinsics(ngp_testbed_t t, int32_t frame_idx, int32_t convert_to_ngp, float* out12);
 /* the depth half of NerfDataset::set_training_image (nerf_loader.cu:907-959; nerf.training.set_image(frame_idx, img, depth_img, depth_scale),
  * python_api.cu:49-67): HOST depth map of view frame_idx, [h][w] uint16 (depth_type 0) or float32 (1), kept on the device as value * depth_scale
  * (scene units along the view axis).  NULL or depth_scale == 0: a map of zeros (no supervision from this view); depth_scale < 0: the view's map is

@@ -350,6 +350,11 @@ int ngp_testbed_set_camera_extrinsics(ngp_testbed_t t, void* stream, int32_t fra
     t->tb.set_camera_extrinsics(S(stream), frame_idx, c2w, convert_to_ngp != 0);
     NGP_API_END
 }
+int ngp_testbed_get_camera_extrinsics(ngp_testbed_t t, int32_t frame_idx, int32_t convert_to_ngp, float* out12) {
+    NGP_API_BEGIN NGP_CHECK(t && out12, "null argument");
+    t->tb.get_camera_extrinsics(frame_idx, convert_to_ngp != 0, out12);
+    NGP_API_END
+}
 int ngp_testbed_set_training_depth(ngp_testbed_t t, void* stream, int32_t frame_idx, const void* host_depth, int32_t depth_type, float depth_scale) {
     NGP_API_BEGIN require_device(); NGP_CHECK(t, "null argument");
     t->tb.set_training_depth(S(stream), frame_idx, host_depth, depth_type, depth_scale);
@@ -556,7 +561,7 @@ int ngp_testbed_debug_buffer(ngp_testbed_t t, const char* name, void** ptr, uint
     X(image_snap_to_pixel_centers, bool) X(image_linear_colors, bool) X(image_random_mode, int) X(sampler_lanes_per_ray, uint32_t) X(prefetch_rays, bool) X(prefetch_hits, uint32_t) X(dp_sharded_optimizer, bool) X(device_control_law, bool) \
     X(exposure, float) X(zoom, float) X(scale, float) X(ground_truth_alpha, float) X(render_near_distance, float) X(fov_axis, int) X(training_view, int)                      \
     X(color_space, int) X(tonemap_curve, int) X(render_mode, int) X(render_ground_truth, bool) X(render_with_lens_distortion, bool) X(render_row_stride, int) X(walk_ahead, bool) X(walk_ahead_hits, uint32_t) X(walk_ahead_misses, uint32_t) \
-    X(optimize_exposure, bool) X(exposure_l2_reg, float) X(n_steps_between_cam_updates, uint32_t) X(max_level_rand_training, bool) X(depth_supervision_lambda, float) X(depth_loss_type, int)
+    X(optimize_exposure, bool) X(exposure_l2_reg, float) X(n_steps_between_cam_updates, uint32_t) X(max_level_rand_training, bool) X(depth_supervision_lambda, float) X(depth_loss_type, int) X(optimize_extrinsics, bool) X(extrinsic_l2_reg, float) X(extrinsic_learning_rate, float)
 
 int ngp_testbed_set_option(ngp_testbed_t t, const char* name, double value) {
     NGP_API_BEGIN NGP_CHECK(t && name, "null argument");

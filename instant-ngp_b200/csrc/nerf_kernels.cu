@@ -1342,6 +1342,43 @@ void nerf_compute_loss(cudaStream_t s, uint32_t n_rays, Aabb aabb, uint32_t n_ra
     NGP_POST_LAUNCH();
 }
 
+__global__ void cam_gradient_kernel(Aabb aabb, uint32_t n_images, uint32_t ray_offset, uint32_t n_rays_global, SamplerBuffers sb,
+                                    const float* __restrict__ coords, const float* __restrict__ coords_gradient, float* __restrict__ cam_pos_gradient,
+                                    float* __restrict__ cam_rot_gradient) {
+    const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x;
+    if (i >= sb.counters[0]) return;
+    const uint32_t numsteps = sb.numsteps[i * 2 + 0];
+    if (numsteps == 0) return;                                  // "The ray doesn't matter. So no gradient onto the camera" (:2045-2048)
+    const uint32_t base = sb.numsteps[i * 2 + 1];
+    const uint32_t img = image_idx(ray_offset + sb.ray_indices[i], n_rays_global, n_images);
+    const V3 ray_o = ld3(sb.rays + (size_t)i * 6), ray_d = normalize3(ld3(sb.rays + (size_t)i * 6 + 3));
+    const V3 wpd = v3(1.0f / (aabb.max[0] - aabb.min[0]), 1.0f / (aabb.max[1] - aabb.min[1]), 1.0f / (aabb.max[2] - aabb.min[2]));   // warp_position_derivative (:397-405)
+    V3 go = v3(0, 0, 0), gd = v3(0, 0, 0);
+    for (uint32_t j = 0; j < numsteps; ++j) {
+        const float* c = coords + (size_t)(base + j) * 7; const float* g = coords_gradient + (size_t)(base + j) * 7;
+        const V3 pos_gradient = v3(g[0] * wpd.x, g[1] * wpd.y, g[2] * wpd.z);
+        go = go + pos_gradient;
+        const V3 pos = unwarp_position(v3(c[0], c[1], c[2]), aabb);
+        const float t = length3(pos - ray_o);                   // "further-away objects' position changes more rapidly as the direction changes"
+        const V3 dir_gradient = v3(g[4] * 0.5f, g[5] * 0.5f, g[6] * 0.5f);   // warp_direction_derivative (:415-417)
+        gd = gd + t * pos_gradient + dir_gradient;
+    }
+    if (cam_pos_gradient) { atomicAdd(cam_pos_gradient + img * 3, go.x); atomicAdd(cam_pos_gradient + img * 3 + 1, go.y); atomicAdd(cam_pos_gradient + img * 3 + 2, go.z); }
+    if (cam_rot_gradient) {                                     // averaged in log space: angle_axis = cross(ray.d, ray_gradient.d) (:2110-2122)
+        const V3 aa = v3(ray_d.y * gd.z - ray_d.z * gd.y, ray_d.z * gd.x - ray_d.x * gd.z, ray_d.x * gd.y - ray_d.y * gd.x);
+        atomicAdd(cam_rot_gradient + img * 3, aa.x); atomicAdd(cam_rot_gradient + img * 3 + 1, aa.y); atomicAdd(cam_rot_gradient + img * 3 + 2, aa.z);
+    }
+}
+void nerf_compute_cam_gradient(cudaStream_t s, uint32_t n_rays_bound, Aabb aabb, uint32_t n_images, uint32_t ray_offset, uint32_t n_rays_global,
+                               const SamplerBuffers& sb, const float* coords_compacted, const float* coords_gradient, float* cam_pos_gradient,
+                               float* cam_rot_gradient) {
+    if (n_rays_bound == 0) return;
+    NGP_PROFILE_SCOPE(s, "cam_gradient", n_rays_bound);
+    cam_gradient_kernel<<<div_round_up(n_rays_bound, 128), 128, 0, s>>>(aabb, n_images, ray_offset, n_rays_global, sb, coords_compacted, coords_gradient, cam_pos_gradient,
+                                                                      cam_rot_gradient);
+    NGP_POST_LAUNCH();
+}
+
 // max_level of the un-compacted samples (testbed_nerf.cu:1438,1652-1657), one thread per kept ray: the rng stream of the ray is replayed up to
 // the draw that follows the pixel position
 __global__ void fill_max_level_kernel(Pcg32 rng, uint32_t n_images, const ImageMeta* __restrict__ metas, bool snap, uint32_t ray_offset, uint32_t n_rays_global,

@@ -96,6 +96,13 @@ struct LossBuffers {
     const __half* enc_in; __half* enc_out; uint32_t enc_width;
     float* max_level_compacted;     // [max_compacted] level cut-off of each kept sample (max_level_rand_training, :1915-1917) or nullptr
 };
+// compute_cam_gradient_train_nerf (testbed_nerf.cu:2014-2123), the extrinsics part: per kept ray the input gradients of its compacted samples
+// (coords_gradient [*][7]: position cols 0..2, direction cols 4..6) are summed into dL/d(ray origin) and dL/d(ray direction); the origin part is
+// added to cam_pos_gradient[image], cross(ray direction, direction part) to cam_rot_gradient[image] (angle-axis, log space).  Run behind the
+// backward pass; numsteps are the COMPACTED (count, base) pairs the loss kernel left.
+void nerf_compute_cam_gradient(cudaStream_t s, uint32_t n_rays_bound, Aabb aabb, uint32_t n_images, uint32_t ray_offset, uint32_t n_rays_global,
+                               const SamplerBuffers& sb, const float* coords_compacted, const float* coords_gradient, float* cam_pos_gradient,
+                               float* cam_rot_gradient);
 void nerf_compute_loss(cudaStream_t s, uint32_t n_rays, Aabb aabb, uint32_t n_rays_total, Pcg32 rng, uint32_t max_samples_compacted,
                        const LossConfig& cfg, uint32_t n_images, const ImageMeta* metas, const float* mean_density_dev,
                        uint32_t ray_offset, uint32_t n_rays_global, const SamplerBuffers& sb, const LossBuffers& lb);

@@ -198,10 +198,15 @@ void Testbed::set_nerf_dataset(cudaStream_t s, uint32_t n_images, const HostImag
         memcpy(m.principal_point, h.principal_point, sizeof(m.principal_point)); memcpy(m.focal_length, h.focal_length, sizeof(m.focal_length));
         memcpy(m.xform, h.xform, sizeof(m.xform)); memcpy(m.xform_end, h.xform, sizeof(m.xform_end));   // start == end, shutter (0,0,0,0)
     }
+    // the poses as given; what the kernels see goes through update_transforms (normalisation of scaled rotations, trained offsets)
+    m_base_xforms.resize(n_images);
+    for (uint32_t i = 0; i < n_images; ++i) { memcpy(m_base_xforms[i].data(), metas[i].xform, 48); memcpy(m_base_xforms[i].data() + 12, metas[i].xform_end, 48); }
+    m_cam_pos_offset.assign(n_images, VecAdam{}); m_cam_rot_offset.assign(n_images, VecAdam{});   // load_nerf_post (testbed_nerf.cu:3036-3039)
+    m_host_metas = metas; m_n_images = n_images;
+    for (uint32_t i = 0; i < n_images; ++i) effective_xform(i, m_host_metas[i].xform, m_host_metas[i].xform_end);
     ImageMeta* md = m_metas.get<ImageMeta>(n_images);
-    NGP_CUDA_CHECK(cudaMemcpyAsync(md, metas.data(), n_images * sizeof(ImageMeta), cudaMemcpyHostToDevice, s));
+    NGP_CUDA_CHECK(cudaMemcpyAsync(md, m_host_metas.data(), n_images * sizeof(ImageMeta), cudaMemcpyHostToDevice, s));
     NGP_CUDA_CHECK(cudaStreamSynchronize(s));
-    m_n_images = n_images; m_host_metas = metas;
     load_nerf_post(s, aabb_scale);
 }
 
@@ -238,6 +243,10 @@ void Testbed::reset(bool reset_density_grid) {
     NGP_CUDA_CHECK(cudaDeviceSynchronize());
     m_prefetch_valid = false; m_early_prefetch = false; m_walk_ahead_valid = false;
     m_cam_exposure_n = 0; m_n_steps_since_cam_update = 0;   // reset_network -> reset_camera_extrinsics (testbed.cu:3921): exposure optimisers start over
+    if (m_n_images && !m_cam_pos_offset.empty()) {          // ... and the pose offsets (testbed_nerf.cu:2921-2933); the given poses are in force again
+        m_cam_pos_offset.assign(m_n_images, VecAdam{}); m_cam_rot_offset.assign(m_n_images, VecAdam{});
+        update_transforms(0, 0, m_n_images);
+    }
     reset_network(reset_density_grid);
 }
 
@@ -293,7 +302,7 @@ void Testbed::set_camera_extrinsics_rolling_shutter(cudaStream_t s, int frame_id
     NGP_CHECK(m_mode == MODE_TB_NERF && c2w_start && c2w_end && rolling_shutter4, "set_camera_extrinsics_rolling_shutter: testbed is not in Nerf mode / null argument");
     if (frame_idx < 0 || frame_idx >= (int)m_n_images) return;   // :2897-2899
     const float* src[2] = {c2w_start, c2w_end};
-    float* dst[2] = {m_host_metas[frame_idx].xform, m_host_metas[frame_idx].xform_end};
+    float* dst[2] = {m_base_xforms[frame_idx].data(), m_base_xforms[frame_idx].data() + 12};
     for (int k = 0; k < 2; ++k) {
         float m[12]; memcpy(m, src[k], sizeof(m));
         if (convert_to_ngp) {   // nerf_matrix_to_ngp (nerf_loader.h:120-140)
@@ -304,8 +313,122 @@ void Testbed::set_camera_extrinsics_rolling_shutter(cudaStream_t s, int frame_id
         memcpy(dst[k], m, sizeof(m));
     }
     memcpy(m_host_metas[frame_idx].rolling_shutter, rolling_shutter4, 16);
-    upload_view_metadata(s, (uint32_t)frame_idx);
+    m_cam_pos_offset[frame_idx] = VecAdam{}; m_cam_rot_offset[frame_idx] = VecAdam{};   // :2908-2911 (the exposure of the view is reset there too)
+    if (m_cam_exposure_n == m_n_images && m_n_images) {
+        NGP_CUDA_CHECK(cudaMemsetAsync(m_cam_exposure.as<float>() + (size_t)frame_idx * 3, 0, 12, s));
+        NGP_CUDA_CHECK(cudaMemsetAsync(m_cam_exposure_m1.as<float>() + (size_t)frame_idx * 3, 0, 12, s));
+        NGP_CUDA_CHECK(cudaMemsetAsync(m_cam_exposure_m2.as<float>() + (size_t)frame_idx * 3, 0, 12, s));
+    }
+    update_transforms(s, (uint32_t)frame_idx, (uint32_t)frame_idx + 1);
 }
+
+// rotmat / rotvec (common_device.cuh:698-722; glm angle / axis, ext/quaternion_trigonometric.inl:5-29), column-major 3x3
+static void rotmat3(const float* v, float* m) {
+    const float angle = std::sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
+    if (angle == 0.0f) { const float id[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}; memcpy(m, id, sizeof(id)); return; }
+    const float x = v[0] / angle, y = v[1] / angle, z = v[2] / angle, sn = sinf(angle), c = cosf(angle), oc = 1.0f - c;
+    const float r[9] = {oc * x * x + c, oc * x * y + z * sn, oc * z * x - y * sn, oc * x * y - z * sn, oc * y * y + c, oc * y * z + x * sn,
+                        oc * z * x + y * sn, oc * y * z - x * sn, oc * z * z + c};
+    memcpy(m, r, sizeof(r));
+}
+static void rotvec3(const float* m, float* v) {
+    float q[4]; quat_cast3(m, q);   // (w, x, y, z)
+    float angle;
+    if (std::fabs(q[0]) > 0.877582561890372716130286068203503191f) {   // cos_one_over_two
+        const float a = asinf(std::sqrt(q[1] * q[1] + q[2] * q[2] + q[3] * q[3])) * 2.0f;
+        angle = q[0] < 0.0f ? 3.14159265358979323846264338327950288f * 2.0f - a : a;
+    } else angle = acosf(q[0]) * 2.0f;
+    const float t1 = 1.0f - q[0] * q[0];
+    float ax[3] = {0.f, 0.f, 1.f};
+    if (t1 > 0.0f) { const float t2 = 1.0f / std::sqrt(t1); ax[0] = q[1] * t2; ax[1] = q[2] * t2; ax[2] = q[3] * t2; }
+    for (int k = 0; k < 3; ++k) v[k] = ax[k] * angle;
+}
+static void mat3_mul(const float* a, const float* b, float* out) {   // column major: out = a * b
+    float r[9];
+    for (int c = 0; c < 3; ++c) for (int rr = 0; rr < 3; ++rr) r[c * 3 + rr] = a[0 * 3 + rr] * b[c * 3 + 0] + a[1 * 3 + rr] * b[c * 3 + 1] + a[2 * 3 + rr] * b[c * 3 + 2];
+    memcpy(out, r, sizeof(r));
+}
+
+// NerfDataset xforms -> training transforms (Testbed::Nerf::Training::update_transforms, testbed_nerf.cu:2984-3023): a rotation block with a
+// scaling component (|det - 1| > 0.01) is normalised by cbrt(det) (and stays normalised), then the view's trained rotation offset is applied
+// from the left and its position offset added
+void Testbed::effective_xform(uint32_t i, float* start, float* end) {
+    float* base[2] = {m_base_xforms[i].data(), m_base_xforms[i].data() + 12};
+    float det[2];
+    for (int k = 0; k < 2; ++k) {
+        const float* m = base[k];
+        det[k] = m[0] * (m[4] * m[8] - m[7] * m[5]) - m[3] * (m[1] * m[8] - m[7] * m[2]) + m[6] * (m[1] * m[5] - m[4] * m[2]);
+    }
+    if (std::fabs(det[0] - 1.0f) > 0.01f || std::fabs(det[1] - 1.0f) > 0.01f)
+        for (int k = 0; k < 2; ++k) { const float c = std::cbrt(det[k]); for (int e = 0; e < 9; ++e) base[k][e] /= c; }
+    float rot[9]; rotmat3(m_cam_rot_offset[i].var, rot);
+    float* out[2] = {start, end};
+    for (int k = 0; k < 2; ++k) {
+        mat3_mul(rot, base[k], out[k]);
+        for (int r = 0; r < 3; ++r) out[k][9 + r] = base[k][9 + r] + m_cam_pos_offset[i].var[r];
+    }
+}
+void Testbed::update_transforms(cudaStream_t s, uint32_t first, uint32_t last) {
+    last = std::min(last, m_n_images);
+    if (first >= last) return;
+    if (m_aux_stream) NGP_CUDA_CHECK(cudaStreamSynchronize(m_aux_stream));   // a ray prefetch in flight reads the old poses
+    m_prefetch_valid = false; m_walk_ahead_valid = false; m_early_prefetch = false; ++m_dataset_version;
+    for (uint32_t i = first; i < last; ++i) effective_xform(i, m_host_metas[i].xform, m_host_metas[i].xform_end);
+    NGP_CUDA_CHECK(cudaMemcpyAsync(m_metas.as<ImageMeta>() + first, &m_host_metas[first], (size_t)(last - first) * sizeof(ImageMeta), cudaMemcpyHostToDevice, s));
+    NGP_CUDA_CHECK(cudaStreamSynchronize(s));
+}
+void Testbed::get_camera_extrinsics(int frame_idx, bool convert_to_ngp, float* out12) const {   // testbed_nerf.cu:2925-2932
+    NGP_CHECK(m_mode == MODE_TB_NERF && frame_idx >= 0 && frame_idx < (int)m_host_metas.size(), "Invalid frame index");
+    float m[12]; memcpy(m, m_host_metas[frame_idx].xform, sizeof(m));
+    if (convert_to_ngp) {   // ngp_matrix_to_nerf (nerf_loader.h:142-158): the inverse of nerf_matrix_to_ngp
+        float t[12];
+        for (int c = 0; c < 4; ++c) { t[c * 3 + 0] = m[c * 3 + 2]; t[c * 3 + 1] = m[c * 3 + 0]; t[c * 3 + 2] = m[c * 3 + 1]; }
+        for (int r = 0; r < 3; ++r) { t[3 + r] *= -1.f; t[6 + r] *= -1.f; t[9 + r] = (t[9 + r] - m_ds_offset[r]) / m_ds_scale; }
+        memcpy(m, t, sizeof(m));
+    }
+    memcpy(out12, m, sizeof(m));
+}
+
+// The extrinsics half of the camera update in Testbed::train_nerf (testbed_nerf.cu:3780-3808): gradients to the host, one Adam step per view on
+// the position offset (AdamOptimizer<vec3>, adam_optimizer.h:143-150) and on the rotation offset (RotationAdamOptimizer, :238-247: the step is
+// composed with the current rotation in matrix form), both with the decaying extrinsic learning rate, then the new poses go to the device
+static void vec_adam_moments(Testbed::VecAdam& st, const float* g, float lr, float* delta) {
+    ++st.iter;
+    const float actual_lr = lr * std::sqrt(1.0f - std::pow(0.99f, (float)st.iter)) / (1.0f - std::pow(0.9f, (float)st.iter));
+    for (int k = 0; k < 3; ++k) {
+        st.m1[k] = 0.9f * st.m1[k] + (1.0f - 0.9f) * g[k];
+        st.m2[k] = 0.99f * st.m2[k] + (1.0f - 0.99f) * g[k] * g[k];
+        delta[k] = actual_lr * st.m1[k] / (std::sqrt(st.m2[k]) + 1e-8f);
+    }
+}
+void Testbed::extrinsics_step(cudaStream_t s) {
+    std::vector<float> gp((size_t)m_n_images * 3), gr((size_t)m_n_images * 3);
+    NGP_CUDA_CHECK(cudaMemcpyAsync(gp.data(), m_cam_pos_grad.as<float>(), gp.size() * 4, cudaMemcpyDeviceToHost, s));
+    NGP_CUDA_CHECK(cudaMemcpyAsync(gr.data(), m_cam_rot_grad.as<float>(), gr.size() * 4, cudaMemcpyDeviceToHost, s));
+    NGP_CUDA_CHECK(cudaStreamSynchronize(s));
+    const float per_camera_loss_scale = (float)m_n_images / LOSS_SCALE / (float)n_steps_between_cam_updates;
+    const float main_lr = m_trainer->opt.current_lr;
+    for (uint32_t i = 0; i < m_n_images; ++i) {
+        VecAdam& po = m_cam_pos_offset[i]; VecAdam& ro = m_cam_rot_offset[i];
+        float pg[3], rg[3];
+        for (int k = 0; k < 3; ++k) {
+            pg[k] = gp[(size_t)i * 3 + k] * per_camera_loss_scale + po.var[k] * extrinsic_l2_reg;
+            rg[k] = gr[(size_t)i * 3 + k] * per_camera_loss_scale + ro.var[k] * extrinsic_l2_reg;
+        }
+        const float lr_p = std::max(extrinsic_learning_rate * std::pow(0.33f, (float)(po.iter / 128)), main_lr / 1000.0f);
+        const float lr_r = std::max(extrinsic_learning_rate * std::pow(0.33f, (float)(ro.iter / 128)), main_lr / 1000.0f);
+        float d[3];
+        vec_adam_moments(po, pg, lr_p, d);
+        for (int k = 0; k < 3; ++k) po.var[k] -= d[k];
+        vec_adam_moments(ro, rg, lr_r, d);
+        const float neg[3] = {-d[0], -d[1], -d[2]};
+        float a[9], b[9], c[9]; rotmat3(neg, a); rotmat3(ro.var, b); mat3_mul(a, b, c);   // variable = rotvec(rotmat(-rot) * rotmat(variable))
+        rotvec3(c, ro.var);
+    }
+    update_transforms(s, 0, m_n_images);
+}
+
+
 
 void Testbed::set_camera_extrinsics(cudaStream_t s, int frame_idx, const float* c2w, bool convert_to_ngp) {   // :2917-2919
     const float zero[4] = {0.f, 0.f, 0.f, 0.f};
@@ -502,10 +625,14 @@ void Testbed::train_end(cudaStream_t s, uint32_t measured_override, uint32_t mea
     m_rays_per_batch = std::min((uint32_t)next_multiple(m_rays_per_batch, BATCH_GRANULARITY), 1u << 18);
     // camera-side optimisers (testbed_nerf.cu:3754-3861; of those this library trains the exposure)
     m_n_steps_since_cam_update += 1;
-    if (optimize_exposure && m_cam_exposure_n == m_n_images && m_n_steps_since_cam_update >= n_steps_between_cam_updates) {
-        const float per_camera_loss_scale = (float)m_n_images / LOSS_SCALE / (float)n_steps_between_cam_updates;
-        nerf_exposure_step(s, m_n_images, m_cam_exposure_grad.as<float>(), m_cam_exposure.as<float>(), m_cam_exposure_m1.as<float>(), m_cam_exposure_m2.as<float>(),
-                           ++m_cam_exposure_iter, m_trainer->opt.current_lr, exposure_l2_reg, per_camera_loss_scale);
+    const bool train_exposure = optimize_exposure && m_cam_exposure_n == m_n_images, train_extrinsics = optimize_extrinsics && m_cam_pos_grad.ptr != nullptr;
+    if ((train_exposure || train_extrinsics) && m_n_steps_since_cam_update >= n_steps_between_cam_updates) {   // :3767-3771
+        if (train_extrinsics) extrinsics_step(s);   // host-side Adam per view, as in the reference; the new poses are on the device before the next sampler runs
+        if (train_exposure) {
+            const float per_camera_loss_scale = (float)m_n_images / LOSS_SCALE / (float)n_steps_between_cam_updates;
+            nerf_exposure_step(s, m_n_images, m_cam_exposure_grad.as<float>(), m_cam_exposure.as<float>(), m_cam_exposure_m1.as<float>(), m_cam_exposure_m2.as<float>(),
+                               ++m_cam_exposure_iter, m_trainer->opt.current_lr, exposure_l2_reg, per_camera_loss_scale);
+        }
         m_n_steps_since_cam_update = 0;
     }
     if (m_walk_ahead_valid) {
@@ -753,6 +880,14 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
             if (m_n_steps_since_cam_update == 0) NGP_CUDA_CHECK(cudaMemsetAsync(lc.exposure_gradient, 0, (size_t)m_n_images * 12, s));   // :3641-3644
         }
     }
+    float* dL_dcoords = nullptr;
+    if (optimize_extrinsics) {   // train_camera (:4071-4073): the backward pass also returns dL/d(coords); per-view accumulators cleared at the start of a window (:3641-3644)
+        NGP_CHECK(!m_comm && m_world == 1, "optimize_extrinsics is not available in data-parallel training");
+        dL_dcoords = m_coords_gradient.get<float>((size_t)target * 7);
+        const bool fresh = m_cam_pos_grad.ptr == nullptr;
+        float* gp = m_cam_pos_grad.get<float>((size_t)m_n_images * 3); float* gr = m_cam_rot_grad.get<float>((size_t)m_n_images * 3);
+        if (fresh || m_n_steps_since_cam_update == 0) { NGP_CUDA_CHECK(cudaMemsetAsync(gp, 0, (size_t)m_n_images * 12, s)); NGP_CUDA_CHECK(cudaMemsetAsync(gr, 0, (size_t)m_n_images * 12, s)); }
+    }
     lb.enc_in = m_nerf_net->last_inference_encoding();   // written by inference() just above
     if (m_copy_pending) { NGP_CUDA_CHECK(cudaStreamWaitEvent(s, m_ev_copy_done, 0)); m_copy_pending = false; }   // uploaded view(s), see set_training_image
     nerf_compute_loss(s, R, aabb, n_rays_total, m_rng, target, lc, m_n_images, m_metas.as<ImageMeta>(), m_mean.as<float>(), ray_offset, n_rays_global, sb, lb);
@@ -765,7 +900,7 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
         const bool next_refreshes_grid = next_step % skip == 0;
         const uint32_t rb = std::min<uint32_t>(1u << 18, (uint32_t)next_multiple((uint64_t)R + R / 2 + BATCH_GRANULARITY, BATCH_GRANULARITY));
         const uint32_t lanes = sampler_lanes_per_ray ? sampler_lanes_per_ray : nerf_sampler_lanes_per_ray(rb);
-        if (device_control_law && prefetch_rays && m_all_images_u8 && !m_comm && m_world == 1 && !next_refreshes_grid && lanes != 1 && !m_walk_ahead_valid) {
+        if (device_control_law && prefetch_rays && m_all_images_u8 && !m_comm && m_world == 1 && !next_refreshes_grid && lanes != 1 && !m_walk_ahead_valid && !optimize_extrinsics) {
             early_rays_bound = rb;
             early_samples_bound = std::min<uint32_t>(max_samples, (uint32_t)next_multiple((uint64_t)max_inference + max_inference / 2 + BATCH_GRANULARITY, BATCH_GRANULARITY));
             StepParams* sp = m_step_params[next_step % N_SETS].get<StepParams>(1);
@@ -806,7 +941,10 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
         NGP_CUDA_CHECK(cudaEventRecord(m_ev_comm_done, m_comm_stream));
         NGP_CUDA_CHECK(cudaStreamWaitEvent(s, m_ev_comm_done, 0));
     } else {
-        m_nerf_net->forward_backward_encoded(s, m_trainer->params, lb.coords_compacted, target, lb.dloss_doutput, m_trainer->grads, m_ev_after_mlp, m_trainer->grid_grads_clean);
+        m_nerf_net->forward_backward_encoded(s, m_trainer->params, lb.coords_compacted, target, lb.dloss_doutput, m_trainer->grads, m_ev_after_mlp, m_trainer->grid_grads_clean,
+                                             nullptr, dL_dcoords);
+        if (dL_dcoords)   // :4098-4124
+            nerf_compute_cam_gradient(s, R, aabb, m_n_images, ray_offset, n_rays_global, sb, lb.coords_compacted, dL_dcoords, m_cam_pos_grad.as<float>(), m_cam_rot_grad.as<float>());
     }
     m_trainer->grid_grads_clean = false;
     m_nerf_net->max_level_gpu = nullptr;   // :4130
@@ -1070,7 +1208,7 @@ void Testbed::debug_buffer(const std::string& name, void** ptr, uint64_t* bytes)
                        {"mlp_out", &m_mlp_out}, {"dloss", &m_dloss}, {"coords_compacted", &m_coords_compacted}, {"loss", &m_loss},
                        {"grid_pos", &m_grid_pos}, {"grid_idx", &m_grid_idx}, {"grid_out", &m_grid_out}, {"density_grid_tmp", &m_density_grid_tmp},
                        {"mean_density", &m_mean}, {"cam_exposure", &m_cam_exposure}, {"cam_exposure_gradient", &m_cam_exposure_grad}, {"numsteps_all", &m_numsteps_all[k]}, {"image_pos", &m_img_pos}, {"image_target", &m_img_target},
-                       {"image_out", &m_img_out}, {"image_dl", &m_img_dl}, {"image", &m_image}, {"max_level", &m_max_level}, {"max_level_compacted", &m_max_level_compacted}, {"sdf_positions", &m_sdf_pos}, {"sdf_distances", &m_sdf_dist}};
+                       {"image_out", &m_img_out}, {"image_dl", &m_img_dl}, {"image", &m_image}, {"max_level", &m_max_level}, {"max_level_compacted", &m_max_level_compacted}, {"cam_pos_gradient", &m_cam_pos_grad}, {"cam_rot_gradient", &m_cam_rot_grad}, {"coords_gradient", &m_coords_gradient}, {"sdf_positions", &m_sdf_pos}, {"sdf_distances", &m_sdf_dist}};
     for (const E& e : table) if (name == e.n) { *ptr = e.b->ptr; *bytes = e.b->bytes; return; }
     throw Error("debug_buffer: unknown buffer '" + name + "'");
 }

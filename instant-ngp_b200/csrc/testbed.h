@@ -9,6 +9,7 @@
 #include "frame_output.h"
 #include "comm.h"
 #include <memory>
+#include <array>
 #include <vector>
 
 namespace ngp {
@@ -41,6 +42,12 @@ public:
     // nerf.training.depth_supervision_lambda / depth_loss_type (testbed.h:726,699; python_api.cu:616,635): weight and loss of the depth term that views
     // with a depth map add to the density gradient (testbed_nerf.cu:1848-1856,1934-1939)
     float depth_supervision_lambda = 0.f; int depth_loss_type = LOSS_L1;
+    // nerf.training.optimize_extrinsics / extrinsic_l2_reg / extrinsic_learning_rate (testbed.h:704,708,709; python_api.cu:624,631,632): per-view
+    // position and rotation offsets trained from the network's input gradients (testbed_nerf.cu:2014-2123,3780-3808,2984-3023)
+    struct VecAdam { uint32_t iter = 0; float m1[3] = {0, 0, 0}, m2[3] = {0, 0, 0}, var[3] = {0, 0, 0}; };   // state of one vec3 optimiser
+    bool optimize_extrinsics = false; float extrinsic_l2_reg = 1e-4f, extrinsic_learning_rate = 1e-3f;
+    // nerf.training.get_camera_extrinsics(frame_idx, convert_to_ngp) (python_api.cu:594-603; testbed_nerf.cu:2925-2932): the view's pose as trained
+    void get_camera_extrinsics(int frame_idx, bool convert_to_ngp, float* out12) const;
     // NerfDataset::set_training_image's depth half (nerf_loader.cu:943-959): host depth map of view frame_idx (depth_type 0: uint16, 1: float32), stored
     // as value * depth_scale; depth_scale <= 0 or a null pointer: a map of zeros ("no depth for this image"); depth_scale < 0 AND null: the map is dropped
     void set_training_depth(cudaStream_t s, int frame_idx, const void* depth_host, int depth_type, float depth_scale);
@@ -237,6 +244,13 @@ private:
     bool adopt_walk_ahead(uint32_t target);
     void launch_early_prefetch(cudaStream_t s, uint32_t target, uint32_t rays_bound, uint32_t samples_bound);
     bool m_prefetch_valid = false, m_all_images_u8 = false; SamplerKey m_prefetch_key{}; uint32_t m_dataset_version = 0, m_last_set = 0;
+    // camera extrinsics optimisation: the poses as given (start, end), the host-side optimiser state per view (AdamOptimizer<vec3> for the position
+    // offset, RotationAdamOptimizer for the rotation offset: adam_optimizer.h:143-301), the device gradient accumulators and dL/d(coords)
+    std::vector<std::array<float, 24>> m_base_xforms; std::vector<VecAdam> m_cam_pos_offset, m_cam_rot_offset;
+    DeviceBuffer m_cam_pos_grad, m_cam_rot_grad, m_coords_gradient;
+    void effective_xform(uint32_t i, float* start12, float* end12);
+    void update_transforms(cudaStream_t s, uint32_t first, uint32_t last);   // NerfDataset xforms + offsets -> the poses the kernels see (testbed_nerf.cu:2984-3023)
+    void extrinsics_step(cudaStream_t s);
     DeviceBuffer m_cam_exposure, m_cam_exposure_grad, m_cam_exposure_m1, m_cam_exposure_m2; uint32_t m_cam_exposure_iter = 0, m_n_steps_since_cam_update = 0, m_cam_exposure_n = 0;
     void ensure_cam_exposure(cudaStream_t s);
     // image mode

@@ -174,9 +174,9 @@ def _stream():
 
 _BOOL_OPTS = {"random_bg_color", "linear_colors", "snap_to_pixel_centers", "train_snap_to_pixel_centers", "shall_train_encoding", "shall_train_network",
               "image_snap_to_pixel_centers", "image_linear_colors", "image_stratified", "prefetch_rays", "dp_sharded_optimizer", "device_control_law",
-              "render_ground_truth", "render_with_lens_distortion", "walk_ahead", "optimize_exposure", "max_level_rand_training"}
+              "render_ground_truth", "render_with_lens_distortion", "walk_ahead", "optimize_exposure", "max_level_rand_training", "optimize_extrinsics"}
 _FLOAT_OPTS = {"near_distance", "density_grid_decay", "render_min_transmittance", "cone_angle_constant", "exposure", "zoom", "fov", "ground_truth_alpha",
-               "render_near_distance", "exposure_l2_reg", "depth_supervision_lambda"}
+               "render_near_distance", "exposure_l2_reg", "depth_supervision_lambda", "extrinsic_l2_reg", "extrinsic_learning_rate"}
 _INT_OPTS = {"loss_type", "rgb_activation", "density_activation", "seed", "sampler_lanes_per_ray", "prefetch_hits", "fov_axis", "walk_ahead_hits", "walk_ahead_misses", "n_steps_between_cam_updates"}
 # enum-valued members (python_api.cu:470,522-523,686): reads come back as the enum
 _ENUM_OPTS = {}     # filled below the enum definitions
@@ -307,9 +307,11 @@ class Testbed:
                                      "snap_to_pixel_centers": "train_snap_to_pixel_centers", "view": "training_view_index",
                                      "optimize_exposure": "optimize_exposure", "exposure_l2_reg": "exposure_l2_reg",
                                      "n_steps_between_cam_updates": "n_steps_between_cam_updates",
-                                     "depth_supervision_lambda": "depth_supervision_lambda", "depth_loss_type": "depth_loss_type"},
+                                     "depth_supervision_lambda": "depth_supervision_lambda", "depth_loss_type": "depth_loss_type",
+                                     "optimize_extrinsics": "optimize_extrinsics", "extrinsic_l2_reg": "extrinsic_l2_reg",
+                                     "extrinsic_learning_rate": "extrinsic_learning_rate"},
                               {"set_image": self.set_training_image, "set_camera_intrinsics": self.set_camera_intrinsics,
-                               "set_camera_extrinsics": self.set_camera_extrinsics,
+                               "set_camera_extrinsics": self.set_camera_extrinsics, "get_camera_extrinsics": self.get_camera_extrinsics,
                                "set_camera_extrinsics_rolling_shutter": self.set_camera_extrinsics_rolling_shutter, "dataset": _Dataset(self),
                                "n_images_for_training": _Lazy(self.n_training_views)})
         object.__setattr__(self, "nerf", _Namespace(self, {"rgb_activation": "rgb_activation", "density_activation": "density_activation",
@@ -663,6 +665,13 @@ class Testbed:
             raise RuntimeError("camera_to_world must be a 3x4 or 4x4 matrix")
         col_major = np.ascontiguousarray(m[:3, :4].T).reshape(-1)
         check(lib().ngp_testbed_set_camera_extrinsics(self._h, _stream(), int(frame_idx), col_major.ctypes.data_as(C.c_void_p), int(convert_to_ngp)))
+
+    def get_camera_extrinsics(self, frame_idx, convert_to_ngp=True):
+        """nerf.training.get_camera_extrinsics(frame_idx, convert_to_ngp=True) (python_api.cu:594-603): the view's pose as trained (3 x 4, rows),
+        in the NeRF convention of transforms.json unless convert_to_ngp is False"""
+        out = (C.c_float * 12)()
+        check(lib().ngp_testbed_get_camera_extrinsics(self._h, int(frame_idx), int(convert_to_ngp), out))
+        return np.array(list(out), np.float32).reshape(4, 3).T.copy()
 
     def set_camera_extrinsics_rolling_shutter(self, frame_idx, camera_to_world_start, camera_to_world_end, rolling_shutter, convert_to_ngp=True):
         """nerf.training.set_camera_extrinsics_rolling_shutter (python_api.cu:606-617): 3x4 (rows) or 4x4 matrices, rolling_shutter = (A, B, C, D)"""

@@ -120,6 +120,29 @@ static void quat_from_mat3(const float* a, float* q) {
         default: q[0] = (m01 - m10) * mult; q[1] = (m20 + m02) * mult; q[2] = (m12 + m21) * mult; q[3] = val; break;
     }
 }
+// rotmat(vec3) / rotvec(mat3) (common_device.cuh:698-722): Rodrigues' formula from an angle-axis vector, and back through glm's quaternion
+// angle() / axis() (dependencies/glm/glm/ext/quaternion_trigonometric.inl:5-29; float32: for small angles 1 - w^2 carries a relative error
+// of several percent, which is part of what the reference's RotationAdamOptimizer computes).  3x3 column major.
+extern "C" void ref_rotmat(const float* v, float* m) {
+    float angle = sqrtf(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
+    if (angle == 0.0f) { for (int i = 0; i < 9; ++i) m[i] = (i % 4 == 0) ? 1.0f : 0.0f; return; }
+    float x = v[0] / angle, y = v[1] / angle, z = v[2] / angle, s = sinf(angle), c = cosf(angle), oc = 1.0f - c;
+    m[0] = oc * x * x + c;     m[1] = oc * x * y + z * s; m[2] = oc * z * x - y * s;
+    m[3] = oc * x * y - z * s; m[4] = oc * y * y + c;     m[5] = oc * y * z + x * s;
+    m[6] = oc * z * x + y * s; m[7] = oc * y * z - x * s; m[8] = oc * z * z + c;
+}
+extern "C" void ref_rotvec(const float* m, float* v) {
+    float q[4]; quat_from_mat3(m, q);
+    float angle;
+    if (fabsf(q[0]) > 0.877582561890372716130286068203503191f) {
+        float a = asinf(sqrtf(q[1] * q[1] + q[2] * q[2] + q[3] * q[3])) * 2.0f;
+        angle = q[0] < 0.0f ? 3.14159265358979323846264338327950288f * 2.0f - a : a;
+    } else angle = acosf(q[0]) * 2.0f;
+    float t1 = 1.0f - q[0] * q[0];
+    float ax[3] = {0.f, 0.f, 1.f};
+    if (t1 > 0.0f) { float t2 = 1.0f / sqrtf(t1); ax[0] = q[1] * t2; ax[1] = q[2] * t2; ax[2] = q[3] * t2; }
+    for (int k = 0; k < 3; ++k) v[k] = ax[k] * angle;
+}
 static float qdot(const float* a, const float* b) { float t0 = a[0] * b[0], t1 = a[1] * b[1], t2 = a[2] * b[2], t3 = a[3] * b[3]; return (t0 + t1) + (t2 + t3); }
 extern "C" void ref_xform_given_rolling_shutter(const float* start, const float* end, const float* rs, float u, float v, float motionblur_time, float* out) {
     float pixel_t = rs[0] + rs[1] * u + rs[2] * v + rs[3] * motionblur_time;
@@ -689,6 +712,37 @@ extern "C" void ref_compute_loss(uint32_t n_rays, const RefAabb* aabb, uint32_t 
         }
     }
     out->compacted_counter = compacted_counter;
+}
+
+// compute_cam_gradient_train_nerf (testbed_nerf.cu:2014-2123), extrinsics part (no distortion map, no focal-length gradient, uv_pdf = 1):
+// numsteps are the compacted (count, base) pairs, coords / coords_gradient the compacted batch [*][7]
+extern "C" void ref_compute_cam_gradient(uint32_t n_rays, const RefAabb* aabb, uint32_t n_images, uint32_t rays_counter, const uint32_t* ray_indices,
+                                         const float* rays, const uint32_t* numsteps, const float* coords, const float* coords_gradient,
+                                         float* cam_pos_gradient, float* cam_rot_gradient) {
+    const uint32_t n_global = g_n_rays_global ? g_n_rays_global : n_rays;
+    for (uint32_t i = 0; i < rays_counter; ++i) {
+        const uint32_t n = numsteps[i * 2], base = numsteps[i * 2 + 1];
+        if (n == 0) continue;
+        const uint32_t img = image_idx(g_ray_offset + ray_indices[i], n_global, n_images);
+        const V3 ray_o = ld3(rays + (size_t)i * 6), ray_d = normalize3(ld3(rays + (size_t)i * 6 + 3));
+        V3 go = v3(0, 0, 0), gd = v3(0, 0, 0);
+        for (uint32_t j = 0; j < n; ++j) {
+            const float* c = coords + (size_t)(base + j) * 7; const float* g = coords_gradient + (size_t)(base + j) * 7;
+            const V3 diag = v3(aabb->max[0] - aabb->min[0], aabb->max[1] - aabb->min[1], aabb->max[2] - aabb->min[2]);
+            const V3 pos_gradient = v3(g[0] * (1.0f / diag.x), g[1] * (1.0f / diag.y), g[2] * (1.0f / diag.z));   // warp_position_derivative
+            go = go + pos_gradient;
+            const V3 pos = unwarp_position(ld3(c), aabb);
+            const float t = length3(pos - ray_o);
+            const V3 dir_gradient = v3(g[4] * 0.5f, g[5] * 0.5f, g[6] * 0.5f);                                       // warp_direction_derivative
+            gd = gd + t * pos_gradient + dir_gradient;
+        }
+        if (cam_pos_gradient) { cam_pos_gradient[img * 3] += go.x; cam_pos_gradient[img * 3 + 1] += go.y; cam_pos_gradient[img * 3 + 2] += go.z; }
+        if (cam_rot_gradient) {
+            cam_rot_gradient[img * 3] += ray_d.y * gd.z - ray_d.z * gd.y;
+            cam_rot_gradient[img * 3 + 1] += ray_d.z * gd.x - ray_d.x * gd.z;
+            cam_rot_gradient[img * 3 + 2] += ray_d.x * gd.y - ray_d.y * gd.x;
+        }
+    }
 }
 
 // fill_rollover_and_rescale / fill_rollover (tcnn common_device; recalled — unpinned): entries [n_input, n_target)

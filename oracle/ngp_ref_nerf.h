@@ -39,6 +39,9 @@ typedef struct RefImage {
 } RefImage;
 // get_xform_given_rolling_shutter (common_device.cuh:401-408) with GLM's quat_cast / slerp / normalize / mat3_cast restated
 // (dependencies/glm/glm/gtc/quaternion.inl:47-72,81-123; ext/quaternion_common.inl:41-73; ext/quaternion_geometric.inl:11-24)
+// rotmat(vec3) / rotvec(mat3) (common_device.cuh:698-722; glm angle / axis): angle-axis vector <-> 3x3 rotation (column major)
+void ref_rotmat(const float* v3, float* m9);
+void ref_rotvec(const float* m9, float* v3);
 void ref_xform_given_rolling_shutter(const float* start, const float* end, const float* rolling_shutter, float u, float v, float motionblur_time, float* out12);
 
 typedef struct RefAabb { float min[3]; float max[3]; } RefAabb;
@@ -119,6 +122,11 @@ void ref_compute_loss(uint32_t n_rays, const RefAabb* aabb, uint32_t n_rays_tota
                       uint32_t max_samples_compacted, uint32_t rays_counter, const RefLossCfg* cfg,
                       uint32_t n_images, const RefImage* images, const uint16_t* network_output /*[..][4]*/,
                       const uint32_t* ray_indices, const float* rays, const float* coords, RefLossOut* out);
+// compute_cam_gradient_train_nerf (testbed_nerf.cu:2014-2123), extrinsics part: per-image sums (+=) of dL/d(ray origin) and of
+// cross(ray direction, dL/d(ray direction)) over the kept rays; numsteps = compacted (count, base), coords / coords_gradient [*][7]
+void ref_compute_cam_gradient(uint32_t n_rays, const RefAabb* aabb, uint32_t n_images, uint32_t rays_counter, const uint32_t* ray_indices,
+                              const float* rays, const uint32_t* numsteps, const float* coords, const float* coords_gradient,
+                              float* cam_pos_gradient, float* cam_rot_gradient);
 // fill_rollover[_and_rescale] (tcnn; testbed_nerf.cu:4061-4069) on [n_target][stride]
 void ref_fill_rollover_half(uint32_t n_target, uint32_t stride, uint32_t n_input, uint16_t* inout, int rescale);
 void ref_fill_rollover_float(uint32_t n_target, uint32_t stride, uint32_t n_input, float* inout);

@@ -334,6 +334,31 @@ def compute_loss(n_rays, aabb, seed, skip, max_compacted, rays_counter, cfg, ima
     return r
 
 
+def rotmat(v):
+    """rotmat(vec3) (common_device.cuh:715-722) -> 3 x 3 (rows)"""
+    v = np.ascontiguousarray(v, np.float32); m = np.zeros(9, np.float32)
+    fn = lib().ref_rotmat; fn.argtypes = [vp, vp]; fn.restype = None
+    fn(P(v), P(m))
+    return m.reshape(3, 3).T.copy()
+
+
+def rotvec(m):
+    """rotvec(mat3) (common_device.cuh:698-701), m 3 x 3 (rows)"""
+    a = np.ascontiguousarray(np.asarray(m, np.float32).T.reshape(-1)); v = np.zeros(3, np.float32)
+    fn = lib().ref_rotvec; fn.argtypes = [vp, vp]; fn.restype = None
+    fn(P(a), P(v))
+    return v
+
+
+def compute_cam_gradient(n_rays, aabb, n_images, rays_counter, ray_indices, rays, numsteps, coords, coords_gradient):
+    """-> (cam_pos_gradient [n_images, 3], cam_rot_gradient [n_images, 3])"""
+    gp = np.zeros((n_images, 3), np.float32); gr = np.zeros((n_images, 3), np.float32)
+    fn = lib().ref_compute_cam_gradient
+    fn.argtypes = [u32, vp, u32, u32, vp, vp, vp, vp, vp, vp, vp]; fn.restype = None
+    fn(n_rays, C.addressof(aabb), n_images, rays_counter, P(ray_indices), P(rays), P(numsteps), P(coords), P(coords_gradient), P(gp), P(gr))
+    return gp, gr
+
+
 def xform_given_rolling_shutter(start, end=None, rolling_shutter=(0, 0, 0, 0), u=0.5, v=0.5, motionblur_time=0.0):
     """get_xform_given_rolling_shutter (common_device.cuh:401-408) -> 12 floats, column major"""
     a = np.ascontiguousarray(np.asarray(start, np.float32).reshape(-1)); b = a if end is None else np.ascontiguousarray(np.asarray(end, np.float32).reshape(-1))

@@ -30,6 +30,15 @@ void shim_get_xform_given_rolling_shutter(const float* start, const float* end, 
     mat4x3 m = get_xform_given_rolling_shutter(x, vec4(rs[0], rs[1], rs[2], rs[3]), vec2(u, v), motionblur_time);
     for (int c = 0; c < 4; ++c) for (int r = 0; r < 3; ++r) out[c * 3 + r] = m[c][r];
 }
+// rotmat(vec3) / rotvec(mat3) (common_device.cuh:698-722), what RotationAdamOptimizer composes its steps with; 3x3 column major [9]
+void shim_rotmat(const float* v, float* out) {
+    mat3 m = rotmat(vec3(v[0], v[1], v[2]));
+    for (int c = 0; c < 3; ++c) for (int r = 0; r < 3; ++r) out[c * 3 + r] = m[c][r];
+}
+void shim_rotvec(const float* in, float* out) {
+    mat3 m; for (int c = 0; c < 3; ++c) for (int r = 0; r < 3; ++r) m[c][r] = in[c * 3 + r];
+    vec3 v = rotvec(m); out[0] = v.x; out[1] = v.y; out[2] = v.z;
+}
 float shim_ld_random_val(uint32_t index, uint32_t seed) { return ld_random_val(index, seed); }
 void shim_ld_random_val_2d(uint32_t index, uint32_t seed, float* out) { vec2 v = ld_random_val_2d(index, seed); out[0] = v.x; out[1] = v.y; }
 float shim_srgb_to_linear(float x) { return srgb_to_linear(x); }

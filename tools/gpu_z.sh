@@ -1,4 +1,4 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 1500 python -m pytest tests/test_ops_gpu.py -x -q -m gpu -k "input_gradients or forward_backward or backward_input" > gpurun_out/z_pytest.txt 2>&1
+timeout 1500 python -m pytest tests/test_extrinsics_gpu.py -q -m gpu -s > gpurun_out/z_pytest.txt 2>&1
 tail -5 gpurun_out/z_pytest.txt
