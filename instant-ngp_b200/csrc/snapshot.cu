@@ -152,7 +152,21 @@ void Testbed::save_snapshot(cudaStream_t s, const std::string& path, bool includ
         rgb["measured_batch_size"] = Json::integer(m_measured);
         rgb["measured_batch_size_before_compaction"] = Json::integer(m_measured_before);
         nerf["rgb"] = rgb;
-        nerf["dataset"] = dataset_json(m_host_metas, render_aabb, m_aabb_scale, !m_all_images_u8, m_ds_scale, m_ds_offset);
+        // the data set keeps the poses as given (NerfDataset::xforms); the trained offsets travel beside them (testbed.cu:4893-4894) and are
+        // applied again by update_transforms when the snapshot is loaded (testbed.cu:5010-5013)
+        std::vector<ImageMeta> given = m_host_metas;
+        for (size_t i = 0; i < given.size() && i < m_base_xforms.size(); ++i) { memcpy(given[i].xform, m_base_xforms[i].data(), 48); memcpy(given[i].xform_end, m_base_xforms[i].data() + 12, 48); }
+        nerf["dataset"] = dataset_json(given, render_aabb, m_aabb_scale, !m_all_images_u8, m_ds_scale, m_ds_offset);
+        const auto opt_json = [](const std::vector<VecAdam>& v, float lr) {   // AdamOptimizer<vec3> / RotationAdamOptimizer::to_json (adam_optimizer.h:177-186,265-274)
+            Json a; a.type = Json::Array;
+            for (const VecAdam& o : v) {
+                Json e; e["iter"] = Json::integer(o.iter); e["first_moment"] = vec_json(o.m1, 3); e["second_moment"] = vec_json(o.m2, 3); e["variable"] = vec_json(o.var, 3);
+                e["learning_rate"] = Json::number(lr); e["epsilon"] = Json::number(1e-8f); e["beta1"] = Json::number(0.9f); e["beta2"] = Json::number(0.99f);
+                a.arr.push_back(e);
+            }
+            return a;
+        };
+        nerf["cam_pos_offset"] = opt_json(m_cam_pos_offset, 1e-4f); nerf["cam_rot_offset"] = opt_json(m_cam_rot_offset, 1e-4f);
         snap["nerf"] = nerf;
     }
     snap["training_step"] = Json::integer(m_training_step);
@@ -160,6 +174,14 @@ void Testbed::save_snapshot(cudaStream_t s, const std::string& path, bool includ
     snap["aabb"] = aabb_json(aabb);
     snap["render_aabb"] = aabb_json(render_aabb);
     snap["background_color"] = vec_json(background_color, 4);
+    // the testbed's own view state (testbed.cu:4903-4913)
+    snap["up_dir"] = vec_json(up_dir, 3);
+    snap["exposure"] = Json::number(exposure);
+    {
+        Json cam; cam["matrix"] = mat4x3_json(camera); cam["fov_axis"] = Json::integer(fov_axis); cam["relative_focal_length"] = vec_json(relative_focal_length, 2);
+        cam["screen_center"] = vec_json(screen_center, 2); cam["zoom"] = Json::number(zoom); cam["scale"] = Json::number(scale);
+        snap["camera"] = cam;
+    }
     Json cfg = m_config; cfg["snapshot"] = snap;
 
     std::string bytes;
@@ -242,6 +264,7 @@ void Testbed::load_snapshot(cudaStream_t s, const std::string& path) {
     if (m_aux_stream) NGP_CUDA_CHECK(cudaStreamSynchronize(m_aux_stream));
     m_prefetch_valid = false;
 
+    bool dataset_from_snapshot = false;
     if (m_mode == MODE_TB_NERF) {
         if ((uint32_t)snap.value("density_grid_size", 0.0) != NERF_GRIDSIZE) throw Error("Incompatible grid size.");
         const Json& nerf = snap.at("nerf");
@@ -269,6 +292,10 @@ void Testbed::load_snapshot(cudaStream_t s, const std::string& path) {
                 if (d.at("xforms").arr.at(i).contains("end")) mat4x3_from_json(d.at("xforms").arr.at(i).at("end"), m.xform_end); else memcpy(m.xform_end, m.xform, sizeof(m.xform));
                 if (md.contains("rolling_shutter") && md.at("rolling_shutter").arr.size() == 4) for (int k = 0; k < 4; ++k) m.rolling_shutter[k] = (float)md.at("rolling_shutter").arr[k].num;
             }
+            m_base_xforms.resize(n_img);
+            for (size_t i = 0; i < n_img; ++i) { memcpy(m_base_xforms[i].data(), m_host_metas[i].xform, 48); memcpy(m_base_xforms[i].data() + 12, m_host_metas[i].xform_end, 48); }
+            m_cam_pos_offset.assign(n_img, VecAdam{}); m_cam_rot_offset.assign(n_img, VecAdam{});
+            dataset_from_snapshot = true;
             aabb_scale = (int)d.value("aabb_scale", (double)aabb_scale);
             m_ds_scale = (float)d.value("scale", (double)m_ds_scale);
             if (d.contains("offset") && d.at("offset").arr.size() == 3) for (int k = 0; k < 3; ++k) m_ds_offset[k] = (float)d.at("offset").arr[k].num;
@@ -281,6 +308,18 @@ void Testbed::load_snapshot(cudaStream_t s, const std::string& path) {
     if (snap.contains("aabb")) aabb_from_json(snap.at("aabb"), aabb);
     if (snap.contains("render_aabb")) aabb_from_json(snap.at("render_aabb"), render_aabb);
     if (snap.contains("background_color")) for (size_t k = 0; k < std::min<size_t>(4, snap.at("background_color").arr.size()); ++k) background_color[k] = (float)snap.at("background_color").arr.at(k).num;
+    // the view state (testbed.cu:5006-5031; "Needs to happen after load_nerf_post()")
+    const auto read_vec = [](const Json& j, float* out, size_t n) { if (j.type == Json::Array && j.arr.size() == n) for (size_t k = 0; k < n; ++k) out[k] = (float)j.arr[k].num; };
+    exposure = (float)snap.value("exposure", (double)exposure);
+    if (snap.contains("up_dir")) read_vec(snap.at("up_dir"), up_dir, 3);
+    if (snap.contains("camera")) {
+        const Json& cam = snap.at("camera");
+        if (cam.contains("matrix")) mat4x3_from_json(cam.at("matrix"), camera);
+        fov_axis = (int)cam.value("fov_axis", (double)fov_axis);
+        if (cam.contains("relative_focal_length")) read_vec(cam.at("relative_focal_length"), relative_focal_length, 2);
+        if (cam.contains("screen_center")) read_vec(cam.at("screen_center"), screen_center, 2);
+        zoom = (float)cam.value("zoom", (double)zoom); scale = (float)cam.value("scale", (double)scale);
+    }
 
     // m_network_config = config; reset_network(false); then counters, Trainer::deserialize (testbed.cu:5028-5040)
     const uint32_t rays_per_batch = m_rays_per_batch, measured = m_measured, measured_before = m_measured_before;
@@ -326,6 +365,32 @@ void Testbed::load_snapshot(cudaStream_t s, const std::string& path) {
             for (uint32_t sc = o.decay_start; sc <= o.step_count && sc < o.decay_end; sc += o.decay_interval) if (sc >= 1) o.current_lr *= o.decay_base;
     }
 
+    if (m_mode == MODE_TB_NERF && snap.at("nerf").contains("dataset")) {
+        // "If the snapshot appears to come from the same dataset as was already present (or none was previously present ...), load dataset-specific
+        // optimized quantities" (testbed.cu:5043-5054): the per-view pose offsets; the poses the kernels see are rebuilt from them
+        const Json& nerf = snap.at("nerf"); const Json& d = nerf.at("dataset");
+        bool same = dataset_from_snapshot;
+        if (!same && (size_t)d.value("n_images", 0.0) == m_base_xforms.size() && d.contains("xforms") && d.at("xforms").arr.size() == m_base_xforms.size()) {
+            same = true;
+            for (size_t i = 0; i < m_base_xforms.size() && same; ++i) { float x[12]; mat4x3_from_json(d.at("xforms").arr[i].at("start"), x); same = memcmp(x, m_base_xforms[i].data(), 48) == 0; }
+        }
+        if (same) {
+            const auto read_opts = [&](const char* key, std::vector<VecAdam>& out) {
+                if (!nerf.contains(key) || nerf.at(key).type != Json::Array || nerf.at(key).arr.size() != out.size()) return;
+                for (size_t i = 0; i < out.size(); ++i) {
+                    const Json& e = nerf.at(key).arr[i]; VecAdam o;
+                    o.iter = (uint32_t)e.value("iter", 0.0);
+                    if (e.contains("first_moment")) read_vec(e.at("first_moment"), o.m1, 3);
+                    if (e.contains("second_moment")) read_vec(e.at("second_moment"), o.m2, 3);
+                    if (e.contains("variable")) read_vec(e.at("variable"), o.var, 3);
+                    out[i] = o;
+                }
+            };
+            read_opts("cam_pos_offset", m_cam_pos_offset); read_opts("cam_rot_offset", m_cam_rot_offset);
+            if (m_n_images) update_transforms(s, 0, m_n_images);
+            else for (size_t i = 0; i < m_host_metas.size(); ++i) effective_xform((uint32_t)i, m_host_metas[i].xform, m_host_metas[i].xform_end);
+        }
+    }
     if (m_mode == MODE_TB_NERF) {
         const Json& g = snap.at("density_grid_binary");
         NGP_CHECK(g.type == Json::Binary, "snapshot: 'density_grid_binary' is not binary");

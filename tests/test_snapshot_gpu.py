@@ -129,3 +129,61 @@ def test_snapshot_errors(env, tmp_path):
     assert "mode" in _lib.lib().ngp_last_error().decode()
     img.load_snapshot(tmp_path / "n.msgpack")
     assert img.mode == pyngp.TestbedMode.Nerf and img.training_step == t.training_step
+
+
+def test_snapshot_carries_view_state_and_trained_camera_offsets(env, tmp_path):
+    """testbed.cu:4893-4894,4902-4913 / :5006-5031,5043-5054: the testbed's own camera, exposure and up vector, and the per-view pose offsets of
+    optimize_extrinsics, which are stored beside the poses as given and applied again on load"""
+    pyngp = env["pyngp"]
+    tb = pyngp.Testbed(pyngp.TestbedMode.Nerf)
+    tb.set_nerf_dataset(env["views"], aabb_scale=1)
+    tb.reload_network_from_json(SMALL_CFG)
+    tb.nerf.training.optimize_extrinsics = True
+    tb.nerf.training.n_steps_between_cam_updates = 4
+    for _ in range(40):
+        tb.train(BATCH)
+    tb.exposure = 0.75
+    tb.up_dir = [0.0, 0.0, 1.0]
+    tb.set_camera_to_training_view(5)
+    tb.zoom = 1.25; tb.screen_center = [0.4, 0.55]; tb.fov_axis = 0; tb.fov = 37.0
+    poses = [tb.get_camera_extrinsics(i, convert_to_ngp=False) for i in range(N_VIEWS)]
+    moved = max(np.abs(p - np.asarray(v["xform"], np.float32).reshape(4, 3).T).max() for p, v in zip(poses, env["views"]))
+    assert moved > 1e-4
+    path = tmp_path / "cams.msgpack"
+    tb.save_snapshot(path)
+    snap = msgpack.unpackb(path.read_bytes(), raw=False)["snapshot"]
+    # the file: poses as given, offsets beside them, view state
+    for i, v in enumerate(env["views"]):
+        given = np.asarray(snap["nerf"]["dataset"]["xforms"][i]["start"], np.float32).T.reshape(-1)
+        assert np.array_equal(given, np.asarray(v["xform"], np.float32))
+    assert len(snap["nerf"]["cam_pos_offset"]) == N_VIEWS and snap["nerf"]["cam_rot_offset"][0]["iter"] == 10
+    assert max(abs(x) for o in snap["nerf"]["cam_rot_offset"] for x in o["variable"]) > 1e-5
+    assert abs(snap["exposure"] - 0.75) < 1e-7 and snap["up_dir"] == [0.0, 0.0, 1.0]
+    assert snap["camera"]["fov_axis"] == 0 and abs(snap["camera"]["zoom"] - 1.25) < 1e-7 and len(snap["camera"]["matrix"]) in (3, 4)
+
+    def check(other):
+        assert abs(other.exposure - 0.75) < 1e-7 and list(other.up_dir) == [0.0, 0.0, 1.0]
+        np.testing.assert_array_equal(other.camera_matrix, tb.camera_matrix)
+        assert other.fov_axis == 0 and abs(other.zoom - 1.25) < 1e-7 and abs(other.fov - 37.0) < 1e-4
+        np.testing.assert_allclose(other.screen_center, [0.4, 0.55], atol=1e-7)
+        np.testing.assert_array_equal(other.relative_focal_length, tb.relative_focal_length)
+        for i in range(N_VIEWS):
+            np.testing.assert_array_equal(other.get_camera_extrinsics(i, convert_to_ngp=False), poses[i])
+
+    fresh = pyngp.Testbed()                                  # no data set: views, offsets and camera all come from the file
+    fresh.load_snapshot(path)
+    check(fresh)
+    same = pyngp.Testbed(pyngp.TestbedMode.Nerf)             # the same data set already loaded: the offsets apply to it
+    same.set_nerf_dataset(env["views"], aabb_scale=1)
+    same.load_snapshot(path)
+    check(same)
+    same.nerf.training.optimize_extrinsics = True
+    for _ in range(8):
+        same.train(BATCH)                                    # and training goes on from the trained poses
+    assert np.isfinite(same.loss)
+    other_data = pyngp.Testbed(pyngp.TestbedMode.Nerf)       # another data set: its own poses stay as they are
+    shifted = [{**v, "xform": np.asarray(v["xform"], np.float32) + np.float32([0] * 9 + [0.01, 0, 0])} for v in env["views"]]
+    other_data.set_nerf_dataset(shifted, aabb_scale=1)
+    other_data.load_snapshot(path)
+    for i, v in enumerate(shifted):
+        np.testing.assert_array_equal(other_data.get_camera_extrinsics(i, convert_to_ngp=False), np.asarray(v["xform"], np.float32).reshape(4, 3).T)
