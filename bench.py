@@ -181,12 +181,14 @@ def cpu_arm(args, views, state, steps, warmup, batch, pretrained_how):
     tr = cpu_train.CpuNerfTrainer(network_config(args.log2_hashmap_size), views)
     if state is not None:
         tr.adopt_state(state)
-    # move to the first step after a refresh at the steady-state cadence (16), keeping the adopted grid
-    tr.training_step = max(tr.training_step, 4096) // 16 * 16 + 1
-    tr.rng_skip = 1 + tr.training_step * (1 << 32)
-    for _ in range(warmup):
+    if state is not None:
+        # move to the first step after a refresh at the steady-state cadence (16), keeping the adopted grid
+        tr.training_step = max(tr.training_step, 4096) // 16 * 16 + 1
+        tr.rng_skip = 1 + tr.training_step * (1 << 32)
+    for _ in range(warmup if state is not None else max(warmup, 1)):   # (no adopted state: the first step builds the occupancy grid)
         tr.train(batch)
-    tr.training_step = tr.training_step // 16 * 16 + 1     # timed steps: none of them refreshes (steps <= 15)
+    if state is not None:
+        tr.training_step = tr.training_step // 16 * 16 + 1     # timed steps: none of them refreshes (steps <= 15)
     tr.timings.clear()
     n = 0; before = 0
     t0 = time.perf_counter()

@@ -564,6 +564,7 @@ class Testbed:
             return self._load_image(os.fspath(first))
         if scene_mode == TestbedMode.Sdf:
             raise RuntimeError("load_mesh: mesh files are not read by this library; hand the (point, distance) records to override_sdf_training_data")
+        os.environ.setdefault("OPENCV_IO_ENABLE_OPENEXR", "1")   # OpenCV reads *.exr only when this is set before its first import
         import cv2
         paths = []
         for p in ([path] if isinstance(path, (str, os.PathLike)) else list(path)):
@@ -616,6 +617,7 @@ class Testbed:
                 h, w = np.frombuffer(f.read(8), np.int32)
                 px = np.frombuffer(f.read(int(h) * int(w) * 8), np.float16).reshape(int(h), int(w), 4).astype(np.float32)
             return self.set_image(px)
+        os.environ.setdefault("OPENCV_IO_ENABLE_OPENEXR", "1")   # OpenCV reads *.exr only when this is set before its first import
         import cv2
         img = cv2.imread(path, cv2.IMREAD_UNCHANGED)
         if img is None:
