@@ -336,6 +336,10 @@ int ngp_testbed_get_vector(ngp_testbed_t t, const char* name, float* values, uin
 int ngp_testbed_set_render_lens(ngp_testbed_t t, int32_t lens_mode, const float* lens_params4);
 /* metadata of training view i as loaded (nerf.training.dataset.metadata[i] + xforms[i]); pixels is the DEVICE copy */
 int ngp_testbed_training_view(ngp_testbed_t t, uint32_t i, ngp_training_image* out);
+/* nerf.training.dataset.transforms[i] / metadata[i].rolling_shutter (python_api.cu:571-581,596): the start and end pose of view i AS GIVEN (NGP convention,
+ * column-major mat4x3; the poses training uses carry the trained offsets on top: ngp_testbed_get_camera_extrinsics) and its rolling-shutter
+ * coefficients; any pointer may be NULL.  The data set's scale / offset / aabb_scale: options "dataset_scale", "dataset_aabb_scale", vector "dataset_offset". */
+int ngp_testbed_training_view_motion(ngp_testbed_t t, uint32_t i, float* xform_start12, float* xform_end12, float* rolling_shutter4);
 uint32_t ngp_testbed_n_training_views(ngp_testbed_t t);
 int ngp_testbed_compute_image_mse(ngp_testbed_t t, void* stream, int32_t quantize_to_byte, float* mse_out);   /* python_api.cu:444 */
 /* runtime knobs (pyngp def_readwrite members, python_api.cu:452-537,611-695); value semantics per name:

@@ -109,6 +109,7 @@ SYMBOLS = {
     "ngp_nerf_dataset_set_image": (i32, [vp, u32, vp, C.c_int32, C.c_int32, C.c_int32]),
     "ngp_nerf_dataset_depth_path": (i32, [vp, u32, cp, u64]),
     "ngp_nerf_dataset_set_depth": (i32, [vp, u32, vp, C.c_int32, C.c_int32]),
+    "ngp_testbed_training_view_motion": (i32, [vp, u32, vp, vp, vp]),
     "ngp_testbed_get_camera_extrinsics": (i32, [vp, C.c_int32, C.c_int32, vp]),
     "ngp_testbed_set_training_depth": (i32, [vp, vp, C.c_int32, vp, C.c_int32, f32]),
     "ngp_nerf_dataset_info": (i32, [vp, C.POINTER(C.c_int32), C.POINTER(f32), C.POINTER(f32), C.POINTER(C.c_int32)]),

@@ -523,6 +523,7 @@ int ngp_testbed_set_vector(ngp_testbed_t t, const char* name, const float* v, ui
 }
 int ngp_testbed_get_vector(ngp_testbed_t t, const char* name, float* v, uint32_t count) {
     NGP_API_BEGIN NGP_CHECK(t && name && v, "null argument");
+    if (std::string(name) == "dataset_offset") { NGP_CHECK(count == 3, "vector option 'dataset_offset' has 3 components"); memcpy(v, t->tb.dataset_offset(), 12); return 0; }   // read-only
     memcpy(v, vector_field(t->tb, name, count), count * sizeof(float));
     NGP_API_END
 }
@@ -540,6 +541,13 @@ int ngp_testbed_training_view(ngp_testbed_t t, uint32_t i, ngp_training_image* o
     o->pixels = m.pixels; o->data_type = m.data_type; o->res[0] = m.res[0]; o->res[1] = m.res[1];
     memcpy(o->focal_length, m.focal_length, 8); memcpy(o->principal_point, m.principal_point, 8);
     o->lens_mode = m.lens_mode; memcpy(o->lens_params, m.lens_params, 16); memcpy(o->xform, m.xform, 48);
+    NGP_API_END
+}
+int ngp_testbed_training_view_motion(ngp_testbed_t t, uint32_t i, float* xform_start12, float* xform_end12, float* rolling_shutter4) {
+    NGP_API_BEGIN NGP_CHECK(t, "null argument"); NGP_CHECK(i < t->tb.training_views().size() && t->tb.given_xform(i), "Invalid frame index");
+    if (xform_start12) memcpy(xform_start12, t->tb.given_xform(i), 48);
+    if (xform_end12) memcpy(xform_end12, t->tb.given_xform(i) + 12, 48);
+    if (rolling_shutter4) memcpy(rolling_shutter4, t->tb.training_views()[i].rolling_shutter, 16);
     NGP_API_END
 }
 int ngp_testbed_compute_image_mse(ngp_testbed_t t, void* stream, int32_t quantize, float* out) {
@@ -590,6 +598,8 @@ int ngp_testbed_get_option(ngp_testbed_t t, const char* name, double* value) {
     if (n == "background_a") { *value = t->tb.background_color[3]; return 0; }
     if (n == "fov") { *value = t->tb.fov(); return 0; }
     if (n == "image_stratified") { *value = t->tb.image_random_mode == IMG_RANDOM_STRATIFIED; return 0; }
+    if (n == "dataset_scale") { *value = t->tb.dataset_scale(); return 0; }              // read-only: nerf.training.dataset.scale / aabb_scale
+    if (n == "dataset_aabb_scale") { *value = t->tb.dataset_aabb_scale(); return 0; }
     if (n == "l2_window_bytes") { *value = t->tb.trainer() ? (double)t->tb.trainer()->l2_window_bytes : 0.0; return 0; }   // read-only
     throw Error("unknown option '" + n + "'");
     NGP_API_END

@@ -70,6 +70,11 @@ public:
     // nerf.training.set_camera_extrinsics_rolling_shutter (python_api.cu:606-617, testbed_nerf.cu:2896-2915): the pose at the start and at the end of the
     // exposure + (A, B, C, D): a ray's camera is interpolated at pixel time A + B u + C v + D motionblur_time (common_device.cuh:401-408)
     void set_camera_extrinsics_rolling_shutter(cudaStream_t s, int frame_idx, const float* c2w_start, const float* c2w_end, const float* rolling_shutter4, bool convert_to_ngp);
+    // NerfDataset::scale / offset / aabb_scale / xforms[i] (nerf_loader.h:73-171) of the loaded data set: the poses as given, before trained offsets
+    float dataset_scale() const { return m_ds_scale; }
+    const float* dataset_offset() const { return m_ds_offset; }
+    int dataset_aabb_scale() const { return m_aabb_scale; }
+    const float* given_xform(uint32_t i) const { return i < m_base_xforms.size() ? m_base_xforms[i].data() : nullptr; }   // [24]: start, end
     void set_dataset_scale_offset(float scale, const float* offset3) { m_ds_scale = scale; for (int k = 0; k < 3; ++k) m_ds_offset[k] = offset3[k]; }
     // Testbed::reset_network(clear_density_grid) (python_api.cu "reset"): fresh parameters, optimizer state, counters
     void reset(bool reset_density_grid);

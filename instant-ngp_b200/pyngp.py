@@ -272,7 +272,7 @@ class _Lazy:
 
 
 class _Dataset:
-    """nerf.training.dataset: n_images, aabb_scale-free view of the loaded metadata (nerf_loader.h:110-171)"""
+    """nerf.training.dataset (NerfDataset, python_api.cu:594-610): n_images, metadata, transforms, scale, offset, aabb_scale, up, render_aabb, paths"""
     def __init__(self, tb):
         self._tb = tb
 
@@ -282,10 +282,52 @@ class _Dataset:
 
     @property
     def metadata(self):
+        tb = self._tb
+
         class M:
-            def __init__(s, v):
+            def __init__(s, i, v):
                 s.resolution = list(v["res"]); s.focal_length = list(v["focal_length"]); s.principal_point = list(v["principal_point"])
-        return [M(self._tb.training_view(i)) for i in range(self.n_images)]
+                rs = (C.c_float * 4)()
+                check(lib().ngp_testbed_training_view_motion(tb._h, i, None, None, rs))
+                s.rolling_shutter = list(rs)
+        return [M(i, self._tb.training_view(i)) for i in range(self.n_images)]
+
+    @property
+    def transforms(self):
+        """TrainingXForm per view: .start / .end, the poses as given (3 x 4, NGP convention)"""
+        class X:
+            pass
+        out = []
+        for i in range(self.n_images):
+            a, b = (C.c_float * 12)(), (C.c_float * 12)()
+            check(lib().ngp_testbed_training_view_motion(self._tb._h, i, a, b, None))
+            x = X(); x.start = np.array(list(a), np.float32).reshape(4, 3).T.copy(); x.end = np.array(list(b), np.float32).reshape(4, 3).T.copy()
+            out.append(x)
+        return out
+
+    @property
+    def scale(self):
+        return float(self._tb.get_option("dataset_scale"))
+
+    @property
+    def aabb_scale(self):
+        return int(self._tb.get_option("dataset_aabb_scale"))
+
+    @property
+    def offset(self):
+        return self._tb._get_vec("dataset_offset", 3)
+
+    @property
+    def up(self):
+        return self._tb.up_dir
+
+    @property
+    def render_aabb(self):
+        return self._tb.render_aabb
+
+    @property
+    def paths(self):
+        return [""] * self.n_images            # the pixels arrive decoded (ngp_nerf_dataset_set_image): the library keeps no file names
 
 
 class Testbed:

@@ -58,6 +58,10 @@ def test_run_py_main_flow(pyngp, views, tmp_path):
     testbed.root_dir = str(root)
     testbed.load_file(str(scene_dir))                               # run.py:93-95: a directory is training data, and the mode follows it
     assert testbed.mode == pyngp.TestbedMode.Nerf and testbed.nerf.training.dataset.n_images == N_VIEWS
+    ds = testbed.nerf.training.dataset                                # NerfDataset members (python_api.cu:594-610)
+    assert abs(ds.scale - 0.33) < 1e-7 and np.allclose(ds.offset, 0.5) and ds.aabb_scale == 1 and len(ds.paths) == N_VIEWS
+    assert np.allclose(ds.transforms[3].start, np.asarray(views[3]["xform"], np.float32).reshape(4, 3).T, atol=2e-6)
+    assert np.array_equal(ds.transforms[3].start, ds.transforms[3].end) and ds.metadata[3].rolling_shutter == [0.0, 0.0, 0.0, 0.0]
     testbed.reload_network_from_file("tinier.json")                 # resolved under <root_dir>/configs/nerf/, two parents up
     merged = json.loads(json.dumps(cfg)); merged["encoding"]["log2_hashmap_size"] = 12; merged["loss"] = {"otype": "L2"}
     explicit = pyngp.Testbed(pyngp.TestbedMode.Nerf)
