@@ -569,7 +569,8 @@ int ngp_testbed_debug_buffer(ngp_testbed_t t, const char* name, void** ptr, uint
     X(image_snap_to_pixel_centers, bool) X(image_linear_colors, bool) X(image_random_mode, int) X(sampler_lanes_per_ray, uint32_t) X(prefetch_rays, bool) X(prefetch_hits, uint32_t) X(dp_sharded_optimizer, bool) X(device_control_law, bool) \
     X(exposure, float) X(zoom, float) X(scale, float) X(ground_truth_alpha, float) X(render_near_distance, float) X(fov_axis, int) X(training_view, int)                      \
     X(color_space, int) X(tonemap_curve, int) X(render_mode, int) X(render_ground_truth, bool) X(render_with_lens_distortion, bool) X(render_row_stride, int) X(walk_ahead, bool) X(walk_ahead_hits, uint32_t) X(walk_ahead_misses, uint32_t) \
-    X(optimize_exposure, bool) X(exposure_l2_reg, float) X(n_steps_between_cam_updates, uint32_t) X(max_level_rand_training, bool) X(depth_supervision_lambda, float) X(depth_loss_type, int) X(optimize_extrinsics, bool) X(extrinsic_l2_reg, float) X(extrinsic_learning_rate, float)
+    X(optimize_exposure, bool) X(exposure_l2_reg, float) X(n_steps_between_cam_updates, uint32_t) X(max_level_rand_training, bool) X(depth_supervision_lambda, float) X(depth_loss_type, int) X(optimize_extrinsics, bool) X(extrinsic_l2_reg, float) X(extrinsic_learning_rate, float) \
+    X(sample_focal_plane_proportional_to_error, bool) X(sample_image_proportional_to_error, bool) X(n_steps_between_error_map_updates, uint32_t)
 
 int ngp_testbed_set_option(ngp_testbed_t t, const char* name, double value) {
     NGP_API_BEGIN NGP_CHECK(t && name, "null argument");
@@ -598,6 +599,10 @@ int ngp_testbed_get_option(ngp_testbed_t t, const char* name, double* value) {
     if (n == "background_a") { *value = t->tb.background_color[3]; return 0; }
     if (n == "fov") { *value = t->tb.fov(); return 0; }
     if (n == "image_stratified") { *value = t->tb.image_random_mode == IMG_RANDOM_STRATIFIED; return 0; }
+    if (n == "error_map_width") { *value = t->tb.error_map_res()[0]; return 0; }            // read-only: the lattice of the current error-map window
+    if (n == "error_map_height") { *value = t->tb.error_map_res()[1]; return 0; }
+    if (n == "error_cdf_width") { *value = t->tb.error_cdf_res()[0]; return 0; }            // ... and of the CDFs in use (0: none yet)
+    if (n == "error_cdf_height") { *value = t->tb.error_cdf_res()[1]; return 0; }
     if (n == "dataset_scale") { *value = t->tb.dataset_scale(); return 0; }              // read-only: nerf.training.dataset.scale / aabb_scale
     if (n == "dataset_aabb_scale") { *value = t->tb.dataset_aabb_scale(); return 0; }
     if (n == "l2_window_bytes") { *value = t->tb.trainer() ? (double)t->tb.trainer()->l2_window_bytes : 0.0; return 0; }   // read-only

@@ -292,11 +292,50 @@ NGP_D bool ray_touches_coarse(const uint32_t* __restrict__ coarse, V3 o, V3 d, f
 //   scan            : exclusive prefix of the per-ray counts (replaces atomicAdd(numsteps_counter, numsteps))
 //   pass 2 (write)  : march again, write NerfCoordinate{warped pos, warped dt, warped dir} at base + j
 // =================================================================================================================
-NGP_D uint32_t image_idx(uint32_t base_idx, uint32_t n_rays, uint32_t n_images) {   // :1317-1338 (no error-map cdf)
+// lower bound in a CDF, clamped to the last bin (common.h:268-291)
+NGP_D uint32_t cdf_binary_search(float val, const float* __restrict__ data, uint32_t length) {
+    if (length == 0) return 0;
+    uint32_t first = 0, count = length;
+    while (count > 0) {
+        const uint32_t step = count / 2, it = first + step;
+        if (data[it] < val) { first = it + 1; count -= step + 1; } else count = step;
+    }
+    return min(first, length - 1);
+}
+// image_idx (:1317-1338): views in ray order, or - sample_image_proportional_to_error - drawn from the view CDF with a low-discrepancy number
+NGP_D uint32_t image_idx(uint32_t base_idx, uint32_t n_rays, uint32_t n_images, const float* __restrict__ cdf_img = nullptr, float* pdf = nullptr) {
+    if (cdf_img) {
+        const float sample = ld_random_val(base_idx, 0xdeadbeefu);
+        const uint32_t img = cdf_binary_search(sample, cdf_img, n_images);
+        if (pdf) { const float prev = img > 0 ? cdf_img[img - 1] : 0.0f; *pdf = (cdf_img[img] - prev) * (float)n_images; }
+        return img;
+    }
+    if (pdf) *pdf = 1.0f;
     return ((base_idx * n_images) / n_rays) % n_images;
 }
-NGP_D void random_image_pos_training(Pcg32& rng, const int* res, bool snap, float* uv) {   // :1291-1315
+// sample_cdf_2d (:1232-1263): half of the samples stay uniform, the other half picks a row from cdf_y and a column from that row's CDF
+NGP_D void sample_cdf_2d(float* uv, uint32_t img, const ErrorMapCdf& c, float* pdf) {
+    const float UNIFORM_SAMPLING_FRACTION = 0.5f;
+    if (uv[0] < UNIFORM_SAMPLING_FRACTION) { uv[0] /= UNIFORM_SAMPLING_FRACTION; return; }   // (pdf keeps the caller's 1: the reference leaves it untouched here)
+    uv[0] = (uv[0] - UNIFORM_SAMPLING_FRACTION) / (1.0f - UNIFORM_SAMPLING_FRACTION);
+    const uint32_t rx = (uint32_t)c.res[0], ry = (uint32_t)c.res[1];
+    const float* cy = c.cdf_y + (size_t)img * ry;
+    const uint32_t y = cdf_binary_search(uv[1], cy, ry);
+    float prev = y > 0 ? cy[y - 1] : 0.0f;
+    const float pmf_y = cy[y] - prev;
+    uv[1] = (uv[1] - prev) / pmf_y;
+    const float* cx = c.cdf_x_cond_y + ((size_t)img * ry + y) * rx;
+    const uint32_t x = cdf_binary_search(uv[0], cx, rx);
+    prev = x > 0 ? cx[x - 1] : 0.0f;
+    const float pmf_x = cx[x] - prev;
+    uv[0] = (uv[0] - prev) / pmf_x;
+    if (pdf) *pdf = pmf_x * pmf_y * (float)(rx * ry);
+    uv[0] = ((float)x + uv[0]) / (float)rx; uv[1] = ((float)y + uv[1]) / (float)ry;
+}
+NGP_D void random_image_pos_training(Pcg32& rng, const int* res, bool snap, float* uv, const ErrorMapCdf* cdf = nullptr, uint32_t img = 0, float* pdf = nullptr) {   // :1291-1315
     uv[0] = rng.next_float(); uv[1] = rng.next_float();
+    if (pdf) *pdf = 1.0f;
+    if (cdf && cdf->cdf_x_cond_y) sample_cdf_2d(uv, img, *cdf, pdf);
     if (snap) {
         uv[0] = ((float)clampi((int)(uv[0] * (float)res[0]), 0, res[0] - 1) + 0.5f) / (float)res[0];
         uv[1] = ((float)clampi((int)(uv[1] * (float)res[1]), 0, res[1] - 1) + 0.5f) / (float)res[1];
@@ -449,10 +488,10 @@ __global__ void __launch_bounds__(SCAN_BLOCK) sampler_count_kernel(uint32_t n_ra
     uint32_t numsteps = 0;
     if (i < n_rays) {
         const uint32_t ig = ray_offset + i;
-        const uint32_t img = image_idx(ig, n_rays_global, n_images);
+        const uint32_t img = image_idx(ig, n_rays_global, n_images, b.cdf.cdf_img);
         const ImageMeta& m = metas[img];
         rng.advance((int64_t)((uint64_t)ig * N_MAX_RANDOM_SAMPLES_PER_RAY));
-        float uv[2]; random_image_pos_training(rng, m.res, snap, uv);
+        float uv[2]; random_image_pos_training(rng, m.res, snap, uv, &b.cdf, img);
         float texel[4]; read_rgba(m, uv[0], uv[1], texel);
         if (texel[0] >= 0.0f) {   // negative = masked-away pixel (:1430-1435)
             if (b.max_level_rand) rng.advance(1);             // :1438 the ray's level cut-off (nerf_fill_max_level hands it to the samples)
@@ -696,10 +735,10 @@ __global__ void __launch_bounds__(128) sampler_classify_kernel(uint32_t n_rays, 
     bool candidate = false;
     if (i < n_rays) {   // the Q lanes of a ray build it redundantly (uniform), lane 0 stores
         const uint32_t ig = ray_offset + i;
-        const uint32_t img = image_idx(ig, n_rays_global, n_images);
+        const uint32_t img = image_idx(ig, n_rays_global, n_images, b.cdf.cdf_img);
         const ImageMeta& m = metas[img];
         rng.advance((int64_t)((uint64_t)ig * N_MAX_RANDOM_SAMPLES_PER_RAY));
-        float uv[2]; random_image_pos_training(rng, m.res, snap, uv);
+        float uv[2]; random_image_pos_training(rng, m.res, snap, uv, &b.cdf, img);
         float texel[4]; read_rgba(m, uv[0], uv[1], texel);
         if (texel[0] >= 0.0f) {   // negative = masked-away pixel (:1430-1435)
             if (b.max_level_rand) rng.advance(1);             // :1438 the ray's level cut-off (nerf_fill_max_level hands it to the samples)
@@ -980,9 +1019,10 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_forward_kernel(uint32_t n_ray
         // replay the sampler's RNG stream to recover pixel + background colour (:1757-1780)
         const uint32_t ig = ray_offset + sb.ray_indices[i];
         rng.advance((int64_t)((uint64_t)ig * N_MAX_RANDOM_SAMPLES_PER_RAY));
-        const uint32_t img = image_idx(ig, n_rays_global, n_images);
+        float img_pdf = 1.0f, uv_pdf = 1.0f;
+        const uint32_t img = image_idx(ig, n_rays_global, n_images, EXTRAS ? sb.cdf.cdf_img : nullptr, &img_pdf);
         const ImageMeta& m = metas[img];
-        float uv[2]; random_image_pos_training(rng, m.res, cfg.snap_to_pixel_centers, uv);
+        float uv[2]; random_image_pos_training(rng, m.res, cfg.snap_to_pixel_centers, uv, EXTRAS ? &sb.cdf : nullptr, img, &uv_pdf);
         const float max_level = (EXTRAS && cfg.max_level_rand) ? rng.next_float() * 2.0f : 1.0f;   // :1775 "Multiply by 2 to ensure 50% of training is at max level"
         rng.advance(1);   // motionblur_time
         V3 bg = ld3(cfg.background_color);
@@ -1008,13 +1048,28 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_forward_kernel(uint32_t n_ray
         if (cn == numsteps) rgb_ray = rgb_ray + T * bg;
         float* rs = lb.ray_scratch + (size_t)i * RAY_SCRATCH;
         rs[0] = rgb_ray.x; rs[1] = rgb_ray.y; rs[2] = rgb_ray.z; rs[3] = target.x; rs[4] = target.y; rs[5] = target.z; rs[6] = __uint_as_float(img);
-        if (EXTRAS) rs[7] = max_level;
+        if (EXTRAS) { rs[7] = max_level; rs[10] = uv[0]; rs[11] = uv[1]; rs[12] = img_pdf; rs[13] = uv_pdf; rs[14] = __int_as_float(m.res[0]); rs[15] = __int_as_float(m.res[1]); }
         if (with_depth) { rs[8] = depth_ray; rs[9] = depth_loss_gradient(cfg, m, uv, ld3(sb.rays + (size_t)i * 6 + 3), depth_ray); }
         lb.compacted_numsteps[i] = cn;
     }
     uint32_t total;
     block_exclusive_scan(cn, total);
     if (threadIdx.x == 0) sb.block_steps[blockIdx.x] = total;
+}
+
+// error map (:1869-1900, without the sharpness weighting - sharpened data sets are not loaded): the ray's mean loss splatted bilinearly around its
+// pixel on the error_map lattice of its view.  The clamp of the integer position uses the IMAGE resolution, as the reference does.
+NGP_D void deposit_error(const LossBuffers& lb, uint32_t img, const int* image_res, float u, float v, float mean_loss) {
+    const int ex = lb.error_map_res[0], ey = lb.error_map_res[1];
+    const float px = fminf(fmaxf(u * (float)ex - 0.5f, 0.0f), (float)ex - (1.0f + 1e-4f)), py = fminf(fmaxf(v * (float)ey - 0.5f, 0.0f), (float)ey - (1.0f + 1e-4f));
+    const int ix = (int)px, iy = (int)py;
+    const float wx = px - (float)ix, wy = py - (float)iy;
+    const int x = clampi(ix, 0, image_res[0] - 2), y = clampi(iy, 0, image_res[1] - 2);
+    float* e = lb.error_map + (size_t)img * ex * ey;
+    atomicAdd(e + (size_t)y * ex + x, (1 - wx) * (1 - wy) * mean_loss);
+    atomicAdd(e + (size_t)y * ex + x + 1, wx * (1 - wy) * mean_loss);
+    atomicAdd(e + (size_t)(y + 1) * ex + x, (1 - wx) * wy * mean_loss);
+    atomicAdd(e + (size_t)(y + 1) * ex + x + 1, wx * wy * mean_loss);
 }
 
 template <bool EXTRAS>
@@ -1037,8 +1092,11 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_backward_kernel(uint32_t n_ra
     const V3 ray_o = ld3(sb.rays + (size_t)i * 6);
 
     const LG lg = loss_and_gradient(target, rgb_ray, cfg.loss_type);
-    const float mean_loss = (lg.loss.x + lg.loss.y + lg.loss.z) / 3.0f;
+    float mean_loss = (lg.loss.x + lg.loss.y + lg.loss.z) / 3.0f;
+    const float uv_pdf = EXTRAS ? rs[13] : 1.0f;
+    if (EXTRAS) mean_loss = ((lg.loss.x / (rs[12] * uv_pdf)) + (lg.loss.y / (rs[12] * uv_pdf)) + (lg.loss.z / (rs[12] * uv_pdf))) / 3.0f;   // lg.loss /= img_pdf * uv_pdf (:1846)
     if (lb.loss) lb.loss[i] = mean_loss / (float)n_rays_global;
+    if (EXTRAS && lb.error_map) { const int ires[2] = {__float_as_int(rs[14]), __float_as_int(rs[15])}; deposit_error(lb, __float_as_uint(rs[6]), ires, rs[10], rs[11], mean_loss); }
     const float loss_scale = cfg.loss_scale / (float)n_rays_global;   // :1903
     const float output_l2_reg = cfg.rgb_activation == ACT_EXPONENTIAL ? 1e-4f : 0.0f;
     const float output_l1_reg_density = *mean_density < NERF_MIN_OPTICAL_THICKNESS ? 1e-4f : 0.0f;
@@ -1080,7 +1138,7 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_backward_kernel(uint32_t n_ra
     }
     if (cfg.exposure_gradient) {
 #pragma unroll
-        for (uint32_t c = 0; c < 3; ++c) accumulate_exposure_gradient(cfg, __float_as_uint(rs[6]), c, pick3(lg.grad.x, lg.grad.y, lg.grad.z, c), pick3(target.x, target.y, target.z, c), loss_scale);
+        for (uint32_t c = 0; c < 3; ++c) accumulate_exposure_gradient(cfg, __float_as_uint(rs[6]), c, pick3(lg.grad.x, lg.grad.y, lg.grad.z, c) / uv_pdf, pick3(target.x, target.y, target.z, c), loss_scale);
     }
 }
 
@@ -1166,9 +1224,10 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_forward_group_kernel(uint32_t
         // replay the sampler's RNG stream to recover pixel + background colour (:1757-1780); uniform across the group
         const uint32_t ig = ray_offset + sb.ray_indices[i];
         rng.advance((int64_t)((uint64_t)ig * N_MAX_RANDOM_SAMPLES_PER_RAY));
-        const uint32_t img = image_idx(ig, n_rays_global, n_images);
+        float img_pdf = 1.0f, uv_pdf = 1.0f;
+        const uint32_t img = image_idx(ig, n_rays_global, n_images, EXTRAS ? sb.cdf.cdf_img : nullptr, &img_pdf);
         const ImageMeta& m = metas[img];
-        float uv[2]; random_image_pos_training(rng, m.res, cfg.snap_to_pixel_centers, uv);
+        float uv[2]; random_image_pos_training(rng, m.res, cfg.snap_to_pixel_centers, uv, EXTRAS ? &sb.cdf : nullptr, img, &uv_pdf);
         const float max_level = (EXTRAS && cfg.max_level_rand) ? rng.next_float() * 2.0f : 1.0f;   // :1775
         rng.advance(1);
         V3 bg3 = ld3(cfg.background_color);
@@ -1192,7 +1251,7 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_forward_group_kernel(uint32_t
             rs[lane] = ray_c; rs[3 + lane] = target;
             if (lane == 0) {
                 rs[6] = __uint_as_float(img);
-                if (EXTRAS) rs[7] = max_level;
+                if (EXTRAS) { rs[7] = max_level; rs[10] = uv[0]; rs[11] = uv[1]; rs[12] = img_pdf; rs[13] = uv_pdf; rs[14] = __int_as_float(m.res[0]); rs[15] = __int_as_float(m.res[1]); }
                 if (with_depth) { rs[8] = depth_ray; rs[9] = depth_loss_gradient(cfg, m, uv, ld3(sb.rays + (size_t)i * 6 + 3), depth_ray); }
             }
         }
@@ -1228,8 +1287,11 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_backward_group_kernel(uint32_
     const V3 ray_o = ld3(sb.rays + (size_t)i * 6);
 
     const LG lg = loss_and_gradient(target, rgb_ray, cfg.loss_type);
-    const float mean_loss = (lg.loss.x + lg.loss.y + lg.loss.z) / 3.0f;
+    float mean_loss = (lg.loss.x + lg.loss.y + lg.loss.z) / 3.0f;
+    const float uv_pdf = EXTRAS ? rs[13] : 1.0f;
+    if (EXTRAS) mean_loss = ((lg.loss.x / (rs[12] * uv_pdf)) + (lg.loss.y / (rs[12] * uv_pdf)) + (lg.loss.z / (rs[12] * uv_pdf))) / 3.0f;   // lg.loss /= img_pdf * uv_pdf (:1846)
     if (lb.loss && lane == 0) lb.loss[i] = mean_loss / (float)n_rays_global;
+    if (EXTRAS && lb.error_map && lane == 0) { const int ires[2] = {__float_as_int(rs[14]), __float_as_int(rs[15])}; deposit_error(lb, __float_as_uint(rs[6]), ires, rs[10], rs[11], mean_loss); }
     const float loss_scale = cfg.loss_scale / (float)n_rays_global;
     const float output_l2_reg = cfg.rgb_activation == ACT_EXPONENTIAL ? 1e-4f : 0.0f;
     const float output_l1_reg_density = *mean_density < NERF_MIN_OPTICAL_THICKNESS ? 1e-4f : 0.0f;
@@ -1285,7 +1347,7 @@ __global__ void __launch_bounds__(SCAN_BLOCK) loss_backward_group_kernel(uint32_
         }
     }
     if (cfg.exposure_gradient && lane < 3)   // one channel per lane
-        accumulate_exposure_gradient(cfg, __float_as_uint(rs[6]), lane, pick3(lg.grad.x, lg.grad.y, lg.grad.z, lane), pick3(target.x, target.y, target.z, lane), loss_scale);
+        accumulate_exposure_gradient(cfg, __float_as_uint(rs[6]), lane, pick3(lg.grad.x, lg.grad.y, lg.grad.z, lane) / uv_pdf, pick3(target.x, target.y, target.z, lane), loss_scale);
 }
 
 // one block: the image count is tens to a few thousand, the work is 3 * n_images Adam updates and three means
@@ -1336,7 +1398,7 @@ void nerf_compute_loss(cudaStream_t s, uint32_t n_rays, Aabb aabb, uint32_t n_ra
     uint32_t G = sb.lanes_per_ray == 1 ? 1u : (n_rays <= 65536 ? 32u : 8u);
     if (const char* e = getenv("NGP_LOSS_LANES")) G = (uint32_t)atoi(e);
     const uint32_t blocks = div_round_up(n_rays, SCAN_BLOCK / G);
-    const bool extras = cfg.depth_supervision_lambda > 0.0f || cfg.max_level_rand || lb.max_level_compacted;
+    const bool extras = cfg.depth_supervision_lambda > 0.0f || cfg.max_level_rand || lb.max_level_compacted || lb.error_map || sb.cdf.cdf_x_cond_y || sb.cdf.cdf_img;
 #define NGP_LOSS_FWD(K) K<<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, rng, cfg, n_images, metas, ray_offset, n_rays_global, sb, lb)
 #define NGP_LOSS_BWD(K) K<<<blocks, SCAN_BLOCK, 0, s>>>(n_rays, aabb, max_compacted, cfg, mean_density_dev, n_rays_global, sb, lb)
     if (G == 32) { if (extras) NGP_LOSS_FWD((loss_forward_group_kernel<32, true>)); else NGP_LOSS_FWD((loss_forward_group_kernel<32, false>)); }
@@ -1353,7 +1415,7 @@ void nerf_compute_loss(cudaStream_t s, uint32_t n_rays, Aabb aabb, uint32_t n_ra
 #undef NGP_LOSS_BWD
 }
 
-__global__ void cam_gradient_kernel(Aabb aabb, uint32_t n_images, uint32_t ray_offset, uint32_t n_rays_global, SamplerBuffers sb,
+__global__ void cam_gradient_kernel(Aabb aabb, Pcg32 rng, bool snap, const ImageMeta* __restrict__ metas, uint32_t n_images, uint32_t ray_offset, uint32_t n_rays_global, SamplerBuffers sb,
                                     const float* __restrict__ coords, const float* __restrict__ coords_gradient, float* __restrict__ cam_pos_gradient,
                                     float* __restrict__ cam_rot_gradient) {
     const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x;
@@ -1361,7 +1423,13 @@ __global__ void cam_gradient_kernel(Aabb aabb, uint32_t n_images, uint32_t ray_o
     const uint32_t numsteps = sb.numsteps[i * 2 + 0];
     if (numsteps == 0) return;                                  // "The ray doesn't matter. So no gradient onto the camera" (:2045-2048)
     const uint32_t base = sb.numsteps[i * 2 + 1];
-    const uint32_t img = image_idx(ray_offset + sb.ray_indices[i], n_rays_global, n_images);
+    const uint32_t ig = ray_offset + sb.ray_indices[i];
+    const uint32_t img = image_idx(ig, n_rays_global, n_images, sb.cdf.cdf_img);
+    float uv_pdf = 1.0f;
+    if (sb.cdf.cdf_x_cond_y) {   // the pixel pdf of the ray, from the replayed rng stream (:2083-2086)
+        rng.advance((int64_t)((uint64_t)ig * N_MAX_RANDOM_SAMPLES_PER_RAY));
+        float uv[2]; random_image_pos_training(rng, metas[img].res, snap, uv, &sb.cdf, img, &uv_pdf);
+    }
     const V3 ray_o = ld3(sb.rays + (size_t)i * 6), ray_d = normalize3(ld3(sb.rays + (size_t)i * 6 + 3));
     const V3 wpd = v3(1.0f / (aabb.max[0] - aabb.min[0]), 1.0f / (aabb.max[1] - aabb.min[1]), 1.0f / (aabb.max[2] - aabb.min[2]));   // warp_position_derivative (:397-405)
     V3 go = v3(0, 0, 0), gd = v3(0, 0, 0);
@@ -1374,19 +1442,50 @@ __global__ void cam_gradient_kernel(Aabb aabb, uint32_t n_images, uint32_t ray_o
         const V3 dir_gradient = v3(g[4] * 0.5f, g[5] * 0.5f, g[6] * 0.5f);   // warp_direction_derivative (:415-417)
         gd = gd + t * pos_gradient + dir_gradient;
     }
-    if (cam_pos_gradient) { atomicAdd(cam_pos_gradient + img * 3, go.x); atomicAdd(cam_pos_gradient + img * 3 + 1, go.y); atomicAdd(cam_pos_gradient + img * 3 + 2, go.z); }
+    if (cam_pos_gradient) { atomicAdd(cam_pos_gradient + img * 3, go.x / uv_pdf); atomicAdd(cam_pos_gradient + img * 3 + 1, go.y / uv_pdf); atomicAdd(cam_pos_gradient + img * 3 + 2, go.z / uv_pdf); }
     if (cam_rot_gradient) {                                     // averaged in log space: angle_axis = cross(ray.d, ray_gradient.d) (:2110-2122)
         const V3 aa = v3(ray_d.y * gd.z - ray_d.z * gd.y, ray_d.z * gd.x - ray_d.x * gd.z, ray_d.x * gd.y - ray_d.y * gd.x);
-        atomicAdd(cam_rot_gradient + img * 3, aa.x); atomicAdd(cam_rot_gradient + img * 3 + 1, aa.y); atomicAdd(cam_rot_gradient + img * 3 + 2, aa.z);
+        atomicAdd(cam_rot_gradient + img * 3, aa.x / uv_pdf); atomicAdd(cam_rot_gradient + img * 3 + 1, aa.y / uv_pdf); atomicAdd(cam_rot_gradient + img * 3 + 2, aa.z / uv_pdf);
     }
 }
-void nerf_compute_cam_gradient(cudaStream_t s, uint32_t n_rays_bound, Aabb aabb, uint32_t n_images, uint32_t ray_offset, uint32_t n_rays_global,
-                               const SamplerBuffers& sb, const float* coords_compacted, const float* coords_gradient, float* cam_pos_gradient,
-                               float* cam_rot_gradient) {
+void nerf_compute_cam_gradient(cudaStream_t s, uint32_t n_rays_bound, Aabb aabb, Pcg32 rng, bool snap_to_pixel_centers, const ImageMeta* metas, uint32_t n_images,
+                               uint32_t ray_offset, uint32_t n_rays_global, const SamplerBuffers& sb, const float* coords_compacted, const float* coords_gradient,
+                               float* cam_pos_gradient, float* cam_rot_gradient) {
     if (n_rays_bound == 0) return;
     NGP_PROFILE_SCOPE(s, "cam_gradient", n_rays_bound);
-    cam_gradient_kernel<<<div_round_up(n_rays_bound, 128), 128, 0, s>>>(aabb, n_images, ray_offset, n_rays_global, sb, coords_compacted, coords_gradient, cam_pos_gradient,
-                                                                      cam_rot_gradient);
+    cam_gradient_kernel<<<div_round_up(n_rays_bound, 128), 128, 0, s>>>(aabb, rng, snap_to_pixel_centers, metas, n_images, ray_offset, n_rays_global, sb, coords_compacted,
+                                                                      coords_gradient, cam_pos_gradient, cam_rot_gradient);
+    NGP_POST_LAUNCH();
+}
+
+// construct_cdf_2d / construct_cdf_1d (testbed_nerf.cu:2354-2409)
+__global__ void construct_cdf_2d_kernel(uint32_t n_images, uint32_t height, uint32_t width, const float* __restrict__ data, float* __restrict__ cdf_x_cond_y, float* __restrict__ cdf_y) {
+    const uint32_t y = threadIdx.x + blockIdx.x * blockDim.x, img = threadIdx.y + blockIdx.y * blockDim.y;
+    if (y >= height || img >= n_images) return;
+    const float MIN_PDF = 0.01f;
+    const size_t off = ((size_t)img * height + y) * width;
+    float cum = 0;
+    for (uint32_t x = 0; x < width; ++x) { cum += data[off + x] + 1e-10f; cdf_x_cond_y[off + x] = cum; }
+    cdf_y[(size_t)img * height + y] = cum;
+    const float norm = 1.0f / cum;                           // __frcp_rn
+    for (uint32_t x = 0; x < width; ++x) cdf_x_cond_y[off + x] = (1.0f - MIN_PDF) * cdf_x_cond_y[off + x] * norm + MIN_PDF * (float)(x + 1) / (float)width;
+}
+__global__ void construct_cdf_1d_kernel(uint32_t n_images, uint32_t height, float* __restrict__ cdf_y, float* __restrict__ cdf_img) {
+    const uint32_t img = threadIdx.x + blockIdx.x * blockDim.x;
+    if (img >= n_images) return;
+    const float MIN_PDF = 0.01f;
+    float* c = cdf_y + (size_t)img * height;
+    float cum = 0;
+    for (uint32_t y = 0; y < height; ++y) { cum += c[y]; c[y] = cum; }
+    cdf_img[img] = cum;
+    const float norm = 1.0f / cum;
+    for (uint32_t y = 0; y < height; ++y) c[y] = (1.0f - MIN_PDF) * c[y] * norm + MIN_PDF * (float)(y + 1) / (float)height;
+}
+void nerf_construct_error_cdfs(cudaStream_t s, uint32_t n_images, uint32_t height, uint32_t width, const float* error_map, float* cdf_x_cond_y, float* cdf_y, float* cdf_img) {
+    const dim3 threads(16, 8, 1), blocks(div_round_up(height, threads.x), div_round_up(n_images, threads.y), 1);
+    construct_cdf_2d_kernel<<<blocks, threads, 0, s>>>(n_images, height, width, error_map, cdf_x_cond_y, cdf_y);
+    NGP_POST_LAUNCH();
+    construct_cdf_1d_kernel<<<div_round_up(n_images, 128), 128, 0, s>>>(n_images, height, cdf_y, cdf_img);
     NGP_POST_LAUNCH();
 }
 
@@ -1398,8 +1497,8 @@ __global__ void fill_max_level_kernel(Pcg32 rng, uint32_t n_images, const ImageM
     if (i >= sb.counters[0]) return;
     const uint32_t ig = ray_offset + sb.ray_indices[i];
     rng.advance((int64_t)((uint64_t)ig * N_MAX_RANDOM_SAMPLES_PER_RAY));
-    const ImageMeta& m = metas[image_idx(ig, n_rays_global, n_images)];
-    float uv[2]; random_image_pos_training(rng, m.res, snap, uv);
+    const ImageMeta& m = metas[image_idx(ig, n_rays_global, n_images, sb.cdf.cdf_img)];
+    float uv[2]; random_image_pos_training(rng, m.res, snap, uv);   // (the draws are what matters here, not where they land)
     const float v = rng.next_float() * 2.0f;
     const uint32_t numsteps = sb.numsteps[i * 2 + 0], base = sb.numsteps[i * 2 + 1];
     for (uint32_t j = 0; j < numsteps; ++j) max_level[base + j] = v;

@@ -28,6 +28,14 @@ void nerf_control_law(cudaStream_t s, const uint32_t* counters, uint32_t rays_pe
                       uint32_t samples_bound, StepParams* out_dev);
 
 // ---- training sampler (testbed_nerf.cu:1382-1658), deterministic ray-order compaction ----
+// Error-map importance sampling (testbed.h:733-738; testbed_nerf.cu:1240-1338,2354-2409,3657-3751): piecewise-constant CDFs over an
+// error_map-sized lattice per view (columns given the row, rows) and over the views; null pointers = uniform sampling
+struct ErrorMapCdf {
+    const float* cdf_x_cond_y;   // [n_images][res[1]][res[0]]  (sample_focal_plane_proportional_to_error)
+    const float* cdf_y;          // [n_images][res[1]]
+    const float* cdf_img;        // [n_images]                  (sample_image_proportional_to_error)
+    int res[2];
+};
 struct SamplerBuffers {
     // per generated ray slot [n_rays]
     uint32_t* numsteps_all;     // pass-1 step count of ray i (0: no sample / masked)
@@ -53,6 +61,7 @@ struct SamplerBuffers {
     // max_level_rand_training (testbed_nerf.cu:1438): every ray that passes the mask test draws one more random number (its level cut-off)
     // between the pixel position and the motion-blur time, which shifts everything drawn after it
     uint32_t max_level_rand;
+    ErrorMapCdf cdf;            // all null: uniform pixels, views in ray order
 };
 uint32_t nerf_sampler_lanes_per_ray(uint32_t n_rays);
 // max_level of the un-compacted samples (testbed_nerf.cu:1438,1652-1657): ray i's cut-off = 2 * (the random number after its pixel position), written
@@ -82,7 +91,7 @@ struct LossConfig {
     int depth_loss_type;            // loss of the depth term (ELossType, L1 by default)
     int max_level_rand;             // max_level_rand_training (:1775): one more draw in the replayed rng stream, the value goes to max_level_compacted
 };
-constexpr uint32_t RAY_SCRATCH = 12;
+constexpr uint32_t RAY_SCRATCH = 16;   // + pixel position (2), view pdf, pixel pdf of the ray (error-map sampling)
 struct LossBuffers {
     const __half* network_output;   // [*][4]
     __half* dloss_doutput;          // [max_compacted][4]
@@ -95,14 +104,18 @@ struct LossBuffers {
     // survive compaction, so the training forward pass does not gather the hash grid a second time for the same points
     const __half* enc_in; __half* enc_out; uint32_t enc_width;
     float* max_level_compacted;     // [max_compacted] level cut-off of each kept sample (max_level_rand_training, :1915-1917) or nullptr
+    float* error_map; int error_map_res[2];   // [n_images][res[1]][res[0]] mean ray loss splatted bilinearly at the ray's pixel (:1869-1900) or nullptr
 };
+// construct_cdf_2d + construct_cdf_1d (testbed_nerf.cu:2354-2409): error map -> per-row column CDFs, per-view row CDFs (both floored by MIN_PDF = 0.01
+// of uniform) and the un-normalised per-view mass in cdf_img (the caller turns it into the view CDF on the host, :3729-3743)
+void nerf_construct_error_cdfs(cudaStream_t s, uint32_t n_images, uint32_t height, uint32_t width, const float* error_map, float* cdf_x_cond_y, float* cdf_y, float* cdf_img);
 // compute_cam_gradient_train_nerf (testbed_nerf.cu:2014-2123), the extrinsics part: per kept ray the input gradients of its compacted samples
 // (coords_gradient [*][7]: position cols 0..2, direction cols 4..6) are summed into dL/d(ray origin) and dL/d(ray direction); the origin part is
 // added to cam_pos_gradient[image], cross(ray direction, direction part) to cam_rot_gradient[image] (angle-axis, log space).  Run behind the
 // backward pass; numsteps are the COMPACTED (count, base) pairs the loss kernel left.
-void nerf_compute_cam_gradient(cudaStream_t s, uint32_t n_rays_bound, Aabb aabb, uint32_t n_images, uint32_t ray_offset, uint32_t n_rays_global,
-                               const SamplerBuffers& sb, const float* coords_compacted, const float* coords_gradient, float* cam_pos_gradient,
-                               float* cam_rot_gradient);
+void nerf_compute_cam_gradient(cudaStream_t s, uint32_t n_rays_bound, Aabb aabb, Pcg32 rng, bool snap_to_pixel_centers, const ImageMeta* metas, uint32_t n_images,
+                               uint32_t ray_offset, uint32_t n_rays_global, const SamplerBuffers& sb, const float* coords_compacted, const float* coords_gradient,
+                               float* cam_pos_gradient, float* cam_rot_gradient);
 void nerf_compute_loss(cudaStream_t s, uint32_t n_rays, Aabb aabb, uint32_t n_rays_total, Pcg32 rng, uint32_t max_samples_compacted,
                        const LossConfig& cfg, uint32_t n_images, const ImageMeta* metas, const float* mean_density_dev,
                        uint32_t ray_offset, uint32_t n_rays_global, const SamplerBuffers& sb, const LossBuffers& lb);

@@ -173,6 +173,7 @@ void Testbed::set_nerf_dataset(cudaStream_t s, uint32_t n_images, const HostImag
     if (m_aux_stream) NGP_CUDA_CHECK(cudaStreamSynchronize(m_aux_stream));   // a ray prefetch in flight reads the old images
     if (m_copy_stream) NGP_CUDA_CHECK(cudaStreamSynchronize(m_copy_stream));
     m_cam_exposure_n = 0; m_n_steps_since_cam_update = 0;   // load_nerf_post (testbed_nerf.cu:3036-3046): fresh exposure optimisers
+    m_cdf_valid = false; m_error_map_live = false; m_n_steps_since_error_map_update = 0;   // error map and CDFs belong to the views that were loaded
     m_copy_pending = false;
     m_prefetch_valid = false; m_early_prefetch = false; m_walk_ahead_valid = false; ++m_dataset_version; m_all_images_u8 = true;
     for (void* p : m_image_buffers) cudaFree(p);
@@ -401,6 +402,26 @@ static void vec_adam_moments(Testbed::VecAdam& st, const float* g, float lr, flo
         delta[k] = actual_lr * st.m1[k] / (std::sqrt(st.m2[k]) + 1e-8f);
     }
 }
+void Testbed::update_error_map_cdfs(cudaStream_t s) {
+    m_cdf_res[0] = m_error_map_res[0]; m_cdf_res[1] = m_error_map_res[1];
+    const size_t nxy = (size_t)m_cdf_res[0] * m_cdf_res[1] * m_n_images, ny = (size_t)m_cdf_res[1] * m_n_images;
+    if (m_aux_stream) NGP_CUDA_CHECK(cudaStreamSynchronize(m_aux_stream));        // a sampler in flight may be reading the old CDFs
+    float* cxy = m_cdf_x_cond_y.get<float>(nxy); float* cy = m_cdf_y.get<float>(ny); float* cimg = m_cdf_img.get<float>(m_n_images);
+    nerf_construct_error_cdfs(s, m_n_images, (uint32_t)m_cdf_res[1], (uint32_t)m_cdf_res[0], m_error_map.as<float>(), cxy, cy, cimg);
+    // the view CDF on the host ("single-threaded anyway", :3729-3743): at least MIN_PMF = 0.1 of the mass stays uniform
+    std::vector<float> pmf(m_n_images), cdf(m_n_images);
+    NGP_CUDA_CHECK(cudaMemcpyAsync(pmf.data(), cimg, m_n_images * sizeof(float), cudaMemcpyDeviceToHost, s));
+    NGP_CUDA_CHECK(cudaStreamSynchronize(s));
+    float cum = 0; for (uint32_t i = 0; i < m_n_images; ++i) { cum += pmf[i]; cdf[i] = cum; }
+    const float norm = 1.0f / cum, MIN_PMF = 0.1f;
+    for (uint32_t i = 0; i < m_n_images; ++i) cdf[i] = (1.0f - MIN_PMF) * cdf[i] * norm + MIN_PMF * (float)(i + 1) / (float)m_n_images;
+    NGP_CUDA_CHECK(cudaMemcpyAsync(cimg, cdf.data(), m_n_images * sizeof(float), cudaMemcpyHostToDevice, s));
+    NGP_CUDA_CHECK(cudaStreamSynchronize(s));
+    m_n_steps_since_error_map_update = 0; m_cdf_valid = true; ++m_cdf_version;
+    n_steps_between_error_map_updates = (uint32_t)((float)n_steps_between_error_map_updates * 1.5f);
+    m_prefetch_valid = false; m_walk_ahead_valid = false; m_early_prefetch = false;   // rays drawn from the old CDFs
+}
+
 void Testbed::extrinsics_step(cudaStream_t s) {
     std::vector<float> gp((size_t)m_n_images * 3), gr((size_t)m_n_images * 3);
     NGP_CUDA_CHECK(cudaMemcpyAsync(gp.data(), m_cam_pos_grad.as<float>(), gp.size() * 4, cudaMemcpyDeviceToHost, s));
@@ -624,6 +645,11 @@ void Testbed::train_end(cudaStream_t s, uint32_t measured_override, uint32_t mea
     m_rays_per_batch = (uint32_t)((float)m_rays_per_batch * (float)target / (float)m_measured);
     m_rays_per_batch = std::min((uint32_t)next_multiple(m_rays_per_batch, BATCH_GRANULARITY), 1u << 18);
     // camera-side optimisers (testbed_nerf.cu:3754-3861; of those this library trains the exposure)
+    // "Compute CDFs from the error map" (testbed_nerf.cu:3700-3751)
+    if (m_error_map_live) {
+        m_n_steps_since_error_map_update += 1;
+        if (m_n_steps_since_error_map_update >= n_steps_between_error_map_updates) update_error_map_cdfs(s);
+    }
     m_n_steps_since_cam_update += 1;
     const bool train_exposure = optimize_exposure && m_cam_exposure_n == m_n_images, train_extrinsics = optimize_extrinsics && m_cam_pos_grad.ptr != nullptr;
     if ((train_exposure || train_extrinsics) && m_n_steps_since_cam_update >= n_steps_between_cam_updates) {   // :3767-3771
@@ -677,7 +703,9 @@ TrainStats Testbed::stats() const {
 // ---------------------------------------------------------------------------------------------------------------
 Testbed::SamplerKey Testbed::sampler_key(uint32_t n_rays, uint32_t max_inference, uint32_t target) const {
     return {m_training_step, n_rays, max_inference, target, m_rank, m_world, sampler_lanes_per_ray, m_dataset_version, m_rng.state, m_rng.inc,
-            cone_angle_constant, train_snap_to_pixel_centers, max_level_rand_training};
+            cone_angle_constant, train_snap_to_pixel_centers, max_level_rand_training,
+            // the CDFs the sampler draws from: their version, and which of the two switches use them
+            m_cdf_valid ? (m_cdf_version * 4u + (sample_focal_plane_proportional_to_error ? 1u : 0u) + (sample_image_proportional_to_error ? 2u : 0u)) : 0u};
 }
 
 SamplerBuffers Testbed::sampler_buffers(cudaStream_t s, uint32_t set, uint32_t target, uint32_t n_rays) {
@@ -686,6 +714,11 @@ SamplerBuffers Testbed::sampler_buffers(cudaStream_t s, uint32_t set, uint32_t t
     const uint32_t max_blocks = max_rays / 8 + 1;   // 256 / lanes_per_ray rays per block, lanes_per_ray <= 32
     SamplerBuffers sb{};
     sb.max_level_rand = max_level_rand_training ? 1u : 0u;
+    if (m_cdf_valid) {   // :3963-3967,4027-4031: each switch hands its CDFs to the sampler and to every kernel that replays the ray's rng stream
+        if (sample_focal_plane_proportional_to_error) { sb.cdf.cdf_x_cond_y = m_cdf_x_cond_y.as<float>(); sb.cdf.cdf_y = m_cdf_y.as<float>(); }
+        if (sample_image_proportional_to_error) sb.cdf.cdf_img = m_cdf_img.as<float>();
+        sb.cdf.res[0] = m_cdf_res[0]; sb.cdf.res[1] = m_cdf_res[1];
+    }
     sb.numsteps_all = m_numsteps_all[set].get<uint32_t>(max_rays); sb.block_steps = m_block_steps[set].get<uint32_t>(max_blocks);
     sb.block_rays = m_block_rays[set].get<uint32_t>(max_blocks); sb.ray_tmp = m_ray_tmp[set].get<float>((size_t)max_rays * 8);
     sb.ray_indices = m_ray_indices[set].get<uint32_t>(max_rays); sb.rays = m_rays[set].get<float>((size_t)max_rays * 6);
@@ -880,6 +913,20 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
             if (m_n_steps_since_cam_update == 0) NGP_CUDA_CHECK(cudaMemsetAsync(lc.exposure_gradient, 0, (size_t)m_n_images * 12, s));   // :3641-3644
         }
     }
+    // error map (:3659-3666): sized for the rays one update window brings per view, cleared at the start of the window
+    const bool error_sampling = sample_focal_plane_proportional_to_error || sample_image_proportional_to_error;
+    if (error_sampling) {
+        NGP_CHECK(!m_comm && m_world == 1, "error-map importance sampling is not available in data-parallel training");
+        if (m_n_steps_since_error_map_update == 0 || !m_error_map_live) {
+            const uint32_t n_samples_per_image = (uint32_t)(((uint64_t)n_steps_between_error_map_updates * R) / m_n_images);
+            const int side = (int)(std::sqrt(std::sqrt((float)n_samples_per_image)) * 3.5f);
+            m_error_map_res[0] = std::min(side, m_host_metas[0].res[0]); m_error_map_res[1] = std::min(side, m_host_metas[0].res[1]);
+            const size_t n = (size_t)m_error_map_res[0] * m_error_map_res[1] * m_n_images;
+            NGP_CUDA_CHECK(cudaMemsetAsync(m_error_map.get<float>(n), 0, n * sizeof(float), s));
+            m_error_map_live = true; m_n_steps_since_error_map_update = 0;
+        }
+        lb.error_map = m_error_map.as<float>(); lb.error_map_res[0] = m_error_map_res[0]; lb.error_map_res[1] = m_error_map_res[1];
+    } else m_error_map_live = false;
     float* dL_dcoords = nullptr;
     if (optimize_extrinsics) {   // train_camera (:4071-4073): the backward pass also returns dL/d(coords); per-view accumulators cleared at the start of a window (:3641-3644)
         NGP_CHECK(!m_comm && m_world == 1, "optimize_extrinsics is not available in data-parallel training");
@@ -900,7 +947,7 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
         const bool next_refreshes_grid = next_step % skip == 0;
         const uint32_t rb = std::min<uint32_t>(1u << 18, (uint32_t)next_multiple((uint64_t)R + R / 2 + BATCH_GRANULARITY, BATCH_GRANULARITY));
         const uint32_t lanes = sampler_lanes_per_ray ? sampler_lanes_per_ray : nerf_sampler_lanes_per_ray(rb);
-        if (device_control_law && prefetch_rays && m_all_images_u8 && !m_comm && m_world == 1 && !next_refreshes_grid && lanes != 1 && !m_walk_ahead_valid && !optimize_extrinsics) {
+        if (device_control_law && prefetch_rays && m_all_images_u8 && !m_comm && m_world == 1 && !next_refreshes_grid && lanes != 1 && !m_walk_ahead_valid && !optimize_extrinsics && !error_sampling) {
             early_rays_bound = rb;
             early_samples_bound = std::min<uint32_t>(max_samples, (uint32_t)next_multiple((uint64_t)max_inference + max_inference / 2 + BATCH_GRANULARITY, BATCH_GRANULARITY));
             StepParams* sp = m_step_params[next_step % N_SETS].get<StepParams>(1);
@@ -944,7 +991,8 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
         m_nerf_net->forward_backward_encoded(s, m_trainer->params, lb.coords_compacted, target, lb.dloss_doutput, m_trainer->grads, m_ev_after_mlp, m_trainer->grid_grads_clean,
                                              nullptr, dL_dcoords);
         if (dL_dcoords)   // :4098-4124
-            nerf_compute_cam_gradient(s, R, aabb, m_n_images, ray_offset, n_rays_global, sb, lb.coords_compacted, dL_dcoords, m_cam_pos_grad.as<float>(), m_cam_rot_grad.as<float>());
+            nerf_compute_cam_gradient(s, R, aabb, m_rng, train_snap_to_pixel_centers, m_metas.as<ImageMeta>(), m_n_images, ray_offset, n_rays_global, sb, lb.coords_compacted, dL_dcoords,
+                                      m_cam_pos_grad.as<float>(), m_cam_rot_grad.as<float>());
     }
     m_trainer->grid_grads_clean = false;
     m_nerf_net->max_level_gpu = nullptr;   // :4130
@@ -1208,7 +1256,7 @@ void Testbed::debug_buffer(const std::string& name, void** ptr, uint64_t* bytes)
                        {"mlp_out", &m_mlp_out}, {"dloss", &m_dloss}, {"coords_compacted", &m_coords_compacted}, {"loss", &m_loss},
                        {"grid_pos", &m_grid_pos}, {"grid_idx", &m_grid_idx}, {"grid_out", &m_grid_out}, {"density_grid_tmp", &m_density_grid_tmp},
                        {"mean_density", &m_mean}, {"cam_exposure", &m_cam_exposure}, {"cam_exposure_gradient", &m_cam_exposure_grad}, {"numsteps_all", &m_numsteps_all[k]}, {"image_pos", &m_img_pos}, {"image_target", &m_img_target},
-                       {"image_out", &m_img_out}, {"image_dl", &m_img_dl}, {"image", &m_image}, {"max_level", &m_max_level}, {"max_level_compacted", &m_max_level_compacted}, {"cam_pos_gradient", &m_cam_pos_grad}, {"cam_rot_gradient", &m_cam_rot_grad}, {"coords_gradient", &m_coords_gradient}, {"sdf_positions", &m_sdf_pos}, {"sdf_distances", &m_sdf_dist}};
+                       {"image_out", &m_img_out}, {"image_dl", &m_img_dl}, {"image", &m_image}, {"max_level", &m_max_level}, {"max_level_compacted", &m_max_level_compacted}, {"error_map", &m_error_map}, {"cdf_x_cond_y", &m_cdf_x_cond_y}, {"cdf_y", &m_cdf_y}, {"cdf_img", &m_cdf_img}, {"cam_pos_gradient", &m_cam_pos_grad}, {"cam_rot_gradient", &m_cam_rot_grad}, {"coords_gradient", &m_coords_gradient}, {"sdf_positions", &m_sdf_pos}, {"sdf_distances", &m_sdf_dist}};
     for (const E& e : table) if (name == e.n) { *ptr = e.b->ptr; *bytes = e.b->bytes; return; }
     throw Error("debug_buffer: unknown buffer '" + name + "'");
 }

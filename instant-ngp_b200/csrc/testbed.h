@@ -39,6 +39,11 @@ public:
     // Testbed::m_max_level_rand_training (testbed.h:573, python_api.cu:498): every training ray draws a level cut-off 2u, u uniform in [0,1): its samples
     // are encoded with the hash-grid levels below cut-off * n_levels only (half of the rays keep every level)
     bool max_level_rand_training = false;
+    // nerf.training.sample_focal_plane_proportional_to_error / sample_image_proportional_to_error (testbed.h:733-738; python_api.cu:624-625): pixels
+    // (half of them) and / or views are drawn from CDFs built from an error map, the mean loss of past rays splatted per view; the map is
+    // accumulated while either switch is on and turned into CDFs every n_steps_between_error_map_updates steps (128, growing by 1.5x each time)
+    bool sample_focal_plane_proportional_to_error = false, sample_image_proportional_to_error = false;
+    uint32_t n_steps_between_error_map_updates = 128;
     // nerf.training.depth_supervision_lambda / depth_loss_type (testbed.h:726,699; python_api.cu:616,635): weight and loss of the depth term that views
     // with a depth map add to the density gradient (testbed_nerf.cu:1848-1856,1934-1939)
     float depth_supervision_lambda = 0.f; int depth_loss_type = LOSS_L1;
@@ -71,6 +76,8 @@ public:
     // exposure + (A, B, C, D): a ray's camera is interpolated at pixel time A + B u + C v + D motionblur_time (common_device.cuh:401-408)
     void set_camera_extrinsics_rolling_shutter(cudaStream_t s, int frame_idx, const float* c2w_start, const float* c2w_end, const float* rolling_shutter4, bool convert_to_ngp);
     // NerfDataset::scale / offset / aabb_scale / xforms[i] (nerf_loader.h:73-171) of the loaded data set: the poses as given, before trained offsets
+    const int* error_map_res() const { return m_error_map_res; }
+    const int* error_cdf_res() const { static const int none[2] = {0, 0}; return m_cdf_valid ? m_cdf_res : none; }
     float dataset_scale() const { return m_ds_scale; }
     const float* dataset_offset() const { return m_ds_offset; }
     int dataset_aabb_scale() const { return m_aabb_scale; }
@@ -192,10 +199,10 @@ private:
     void train_image_step(cudaStream_t s, uint32_t batch_size, bool get_loss);                     // testbed_image.cu:214-285
     void train_sdf_step(cudaStream_t s, uint32_t batch_size, bool get_loss);                       // testbed_sdf.cu:1289-1311
     struct SamplerKey {   // everything generate_training_samples depends on besides the bitfield and the view poses
-        uint32_t step, n_rays, max_inference, target, rank, world, lanes, dataset_version; uint64_t rng_state, rng_inc; float cone; bool snap, max_level_rand;
+        uint32_t step, n_rays, max_inference, target, rank, world, lanes, dataset_version; uint64_t rng_state, rng_inc; float cone; bool snap, max_level_rand; uint32_t cdf_version;
         bool operator==(const SamplerKey& o) const {
             return step == o.step && n_rays == o.n_rays && max_inference == o.max_inference && target == o.target && rank == o.rank && world == o.world &&
-                   lanes == o.lanes && dataset_version == o.dataset_version && rng_state == o.rng_state && rng_inc == o.rng_inc && cone == o.cone && snap == o.snap && max_level_rand == o.max_level_rand;
+                   lanes == o.lanes && dataset_version == o.dataset_version && rng_state == o.rng_state && rng_inc == o.rng_inc && cone == o.cone && snap == o.snap && max_level_rand == o.max_level_rand && cdf_version == o.cdf_version;
         }
     };
     SamplerKey sampler_key(uint32_t n_rays, uint32_t max_inference, uint32_t target) const;
@@ -221,6 +228,9 @@ private:
     std::vector<void*> m_image_buffers; std::vector<size_t> m_image_bytes; DeviceBuffer m_metas; std::vector<ImageMeta> m_host_metas;
     DeviceBuffer m_density_grid, m_density_grid_tmp, m_bitfield, m_mean, m_partials, m_grid_pos, m_grid_idx, m_grid_out;
     uint32_t m_density_grid_ema_step = 0; bool m_grid_allocated = false;
+    DeviceBuffer m_error_map, m_cdf_x_cond_y, m_cdf_y, m_cdf_img; int m_error_map_res[2] = {0, 0}, m_cdf_res[2] = {0, 0};
+    uint32_t m_n_steps_since_error_map_update = 0, m_cdf_version = 0; bool m_cdf_valid = false, m_error_map_live = false;
+    void update_error_map_cdfs(cudaStream_t s);
     DeviceBuffer m_max_level, m_max_level_compacted;        // per-sample level cut-offs (max_level_rand_training)
     size_t m_grid_elements = 0;                             // cells of the occupancy grid as allocated (128^3 x cascades in use)
     float m_ds_scale = 0.33f, m_ds_offset[3] = {0.5f, 0.5f, 0.5f};   // NerfDataset::scale / offset (nerf_loader.h:29, nerf_loader.cu:392-393)

@@ -174,10 +174,11 @@ def _stream():
 
 _BOOL_OPTS = {"random_bg_color", "linear_colors", "snap_to_pixel_centers", "train_snap_to_pixel_centers", "shall_train_encoding", "shall_train_network",
               "image_snap_to_pixel_centers", "image_linear_colors", "image_stratified", "prefetch_rays", "dp_sharded_optimizer", "device_control_law",
-              "render_ground_truth", "render_with_lens_distortion", "walk_ahead", "optimize_exposure", "max_level_rand_training", "optimize_extrinsics"}
+              "render_ground_truth", "render_with_lens_distortion", "walk_ahead", "optimize_exposure", "max_level_rand_training", "optimize_extrinsics",
+              "sample_focal_plane_proportional_to_error", "sample_image_proportional_to_error"}
 _FLOAT_OPTS = {"near_distance", "density_grid_decay", "render_min_transmittance", "cone_angle_constant", "exposure", "zoom", "fov", "ground_truth_alpha",
                "render_near_distance", "exposure_l2_reg", "depth_supervision_lambda", "extrinsic_l2_reg", "extrinsic_learning_rate"}
-_INT_OPTS = {"loss_type", "rgb_activation", "density_activation", "seed", "sampler_lanes_per_ray", "prefetch_hits", "fov_axis", "walk_ahead_hits", "walk_ahead_misses", "n_steps_between_cam_updates"}
+_INT_OPTS = {"loss_type", "rgb_activation", "density_activation", "seed", "sampler_lanes_per_ray", "prefetch_hits", "fov_axis", "walk_ahead_hits", "walk_ahead_misses", "n_steps_between_cam_updates", "n_steps_between_error_map_updates"}
 # enum-valued members (python_api.cu:470,522-523,686): reads come back as the enum
 _ENUM_OPTS = {}     # filled below the enum definitions
 _VECTOR_OPTS = {"screen_center": 2, "relative_focal_length": 2, "up_dir": 3, "background_color": 4}
@@ -351,7 +352,10 @@ class Testbed:
                                      "n_steps_between_cam_updates": "n_steps_between_cam_updates",
                                      "depth_supervision_lambda": "depth_supervision_lambda", "depth_loss_type": "depth_loss_type",
                                      "optimize_extrinsics": "optimize_extrinsics", "extrinsic_l2_reg": "extrinsic_l2_reg",
-                                     "extrinsic_learning_rate": "extrinsic_learning_rate"},
+                                     "extrinsic_learning_rate": "extrinsic_learning_rate",
+                                     "sample_focal_plane_proportional_to_error": "sample_focal_plane_proportional_to_error",
+                                     "sample_image_proportional_to_error": "sample_image_proportional_to_error",
+                                     "n_steps_between_error_map_updates": "n_steps_between_error_map_updates"},
                               {"set_image": self.set_training_image, "set_camera_intrinsics": self.set_camera_intrinsics,
                                "set_camera_extrinsics": self.set_camera_extrinsics, "get_camera_extrinsics": self.get_camera_extrinsics,
                                "set_camera_extrinsics_rolling_shutter": self.set_camera_extrinsics_rolling_shutter, "dataset": _Dataset(self),

@@ -478,11 +478,55 @@ extern "C" float ref_update_bitfield(const float* grid, uint32_t n_cascades, uin
 struct RaySetup { bool valid; V3 o, d_unnorm, d; float startt, cone_angle; };
 
 // shared head of generate_training_samples_nerf (testbed_nerf.cu:1417-1499) and of the loss kernel's RNG replay (:1757-1780)
-static inline uint32_t image_idx(uint32_t base_idx, uint32_t n_rays, uint32_t n_images) {   // :1317-1338, cdf == nullptr
+// Error-map importance sampling (testbed.h:733-738; testbed_nerf.cu:1232-1338,1846,1869-1900,1969-1972,2083-2107,2354-2409): a process-wide state
+// for the sampler / loss / camera-gradient functions below.  CDF pointers that are NULL leave that choice uniform; error_map NULL = no splatting.
+static const float* g_cdf_x_cond_y = nullptr; static const float* g_cdf_y = nullptr; static const float* g_cdf_img = nullptr; static int g_cdf_res[2] = {0, 0};
+static float* g_error_map = nullptr; static int g_error_map_res[2] = {0, 0};
+extern "C" void ref_set_error_map(const float* cdf_x_cond_y, const float* cdf_y, const float* cdf_img, int cdf_w, int cdf_h, float* error_map, int map_w, int map_h) {
+    g_cdf_x_cond_y = cdf_x_cond_y; g_cdf_y = cdf_y; g_cdf_img = cdf_img; g_cdf_res[0] = cdf_w; g_cdf_res[1] = cdf_h;
+    g_error_map = error_map; g_error_map_res[0] = map_w; g_error_map_res[1] = map_h;
+}
+static uint32_t binary_search(float val, const float* data, uint32_t length) {   // common.h:268-291
+    if (length == 0) return 0;
+    uint32_t it, count = length, step, first = 0;
+    while (count > 0) {
+        it = first; step = count / 2; it += step;
+        if (data[it] < val) { first = ++it; count -= step + 1; } else count = step;
+    }
+    return std::min(first, length - 1);
+}
+static inline uint32_t image_idx(uint32_t base_idx, uint32_t n_rays, uint32_t n_images, float* pdf = nullptr) {   // :1317-1338
+    if (g_cdf_img) {
+        float sample = ref_ld_random_val(base_idx, 0xdeadbeefu);
+        uint32_t img = binary_search(sample, g_cdf_img, n_images);
+        if (pdf) { float prev = img > 0 ? g_cdf_img[img - 1] : 0.0f; *pdf = (g_cdf_img[img] - prev) * (float)n_images; }
+        return img;
+    }
+    if (pdf) *pdf = 1.0f;
     return ((base_idx * n_images) / n_rays) % n_images;   // uint32 product wraps exactly as in the reference
 }
-static inline void random_image_pos_training(RefPcg32* rng, const int32_t* res, int snap, float* uv) {   // :1291-1315
+static void sample_cdf_2d(float* uv, uint32_t img, float* pdf) {   // :1232-1263
+    const float UNIFORM_SAMPLING_FRACTION = 0.5f;
+    if (uv[0] < UNIFORM_SAMPLING_FRACTION) { uv[0] /= UNIFORM_SAMPLING_FRACTION; return; }
+    uv[0] = (uv[0] - UNIFORM_SAMPLING_FRACTION) / (1.0f - UNIFORM_SAMPLING_FRACTION);
+    const uint32_t rx = (uint32_t)g_cdf_res[0], ry = (uint32_t)g_cdf_res[1];
+    const float* cy = g_cdf_y + (size_t)img * ry;
+    uint32_t y = binary_search(uv[1], cy, ry);
+    float prev = y > 0 ? cy[y - 1] : 0.0f;
+    float pmf_y = cy[y] - prev;
+    uv[1] = (uv[1] - prev) / pmf_y;
+    const float* cx = g_cdf_x_cond_y + (size_t)img * ry * rx + (size_t)y * rx;
+    uint32_t x = binary_search(uv[0], cx, rx);
+    prev = x > 0 ? cx[x - 1] : 0.0f;
+    float pmf_x = cx[x] - prev;
+    uv[0] = (uv[0] - prev) / pmf_x;
+    if (pdf) *pdf = pmf_x * pmf_y * (float)(rx * ry);
+    uv[0] = ((float)x + uv[0]) / (float)rx; uv[1] = ((float)y + uv[1]) / (float)ry;
+}
+static inline void random_image_pos_training(RefPcg32* rng, const int32_t* res, int snap, float* uv, uint32_t img = 0, float* pdf = nullptr) {   // :1291-1315
     uv[0] = ref_pcg32_next_float(rng); uv[1] = ref_pcg32_next_float(rng);
+    if (pdf) *pdf = 1.0f;
+    if (g_cdf_x_cond_y) sample_cdf_2d(uv, img, pdf);
     if (snap) {
         uv[0] = ((float)clampi((int)(uv[0] * (float)res[0]), 0, res[0] - 1) + 0.5f) / (float)res[0];
         uv[1] = ((float)clampi((int)(uv[1] * (float)res[1]), 0, res[1] - 1) + 0.5f) / (float)res[1];
@@ -513,7 +557,7 @@ extern "C" void ref_generate_training_samples(uint32_t n_rays, const RefAabb* aa
         uint32_t img = image_idx(ig, n_global, n_images);
         const RefImage* m = &images[img];
         RefPcg32 rng = base; ref_pcg32_advance(&rng, (int64_t)((uint64_t)ig * REF_N_MAX_RANDOM_SAMPLES_PER_RAY));
-        float uv[2]; random_image_pos_training(&rng, m->res, snap, uv);
+        float uv[2]; random_image_pos_training(&rng, m->res, snap, uv, img);
         float texel[4]; read_rgba(m, uv, texel);
         if (texel[0] < 0.0f) continue;                      // masked-away pixel (:1430-1435)
         const float max_level = g_max_level_rand ? ref_pcg32_next_float(&rng) * 2.0f : 1.0f;   // :1438
@@ -625,9 +669,10 @@ extern "C" void ref_compute_loss(uint32_t n_rays, const RefAabb* aabb, uint32_t 
         // RNG replay (:1757-1780)
         uint32_t ray_idx = g_ray_offset + ray_indices[i];
         RefPcg32 rng = base; ref_pcg32_advance(&rng, (int64_t)((uint64_t)ray_idx * REF_N_MAX_RANDOM_SAMPLES_PER_RAY));
-        uint32_t img = image_idx(ray_idx, n_global, n_images);
+        float img_pdf = 1.0f, uv_pdf = 1.0f;
+        uint32_t img = image_idx(ray_idx, n_global, n_images, &img_pdf);
         const RefImage* m = &images[img];
-        float uv[2]; random_image_pos_training(&rng, m->res, cfg->snap_to_pixel_centers, uv);
+        float uv[2]; random_image_pos_training(&rng, m->res, cfg->snap_to_pixel_centers, uv, img, &uv_pdf);
         const float max_level = g_max_level_rand ? ref_pcg32_next_float(&rng) * 2.0f : 1.0f;   // :1775
         ref_pcg32_advance(&rng, 1);   // motionblur_time
         V3 bg = ld3(cfg->background_color);
@@ -661,8 +706,18 @@ extern "C" void ref_compute_loss(uint32_t n_rays, const RefAabb* aabb, uint32_t 
         if (cn == 0) continue;
 
         LG lg = loss_and_gradient(target, rgb_ray, cfg->loss_type);
+        lg.loss = v3(lg.loss.x / (img_pdf * uv_pdf), lg.loss.y / (img_pdf * uv_pdf), lg.loss.z / (img_pdf * uv_pdf));   // :1846 (the gradient is NOT divided, :1858-1862)
         float mean_loss = (lg.loss.x + lg.loss.y + lg.loss.z) / 3.0f;
         if (out->loss) out->loss[i] = mean_loss / (float)n_global;
+        if (g_error_map) {   // :1869-1900 (no sharpness data)
+            const int ex = g_error_map_res[0], ey = g_error_map_res[1];
+            float px = std::min(std::max(uv[0] * (float)ex - 0.5f, 0.0f), (float)ex - (1.0f + 1e-4f)), py = std::min(std::max(uv[1] * (float)ey - 0.5f, 0.0f), (float)ey - (1.0f + 1e-4f));
+            int ix = (int)px, iy = (int)py; float wx = px - (float)ix, wy = py - (float)iy;
+            int x = clampi(ix, 0, m->res[0] - 2), y = clampi(iy, 0, m->res[1] - 2);
+            float* e = g_error_map + (size_t)img * ex * ey;
+            e[(size_t)y * ex + x] += (1 - wx) * (1 - wy) * mean_loss; e[(size_t)y * ex + x + 1] += wx * (1 - wy) * mean_loss;
+            e[(size_t)(y + 1) * ex + x] += (1 - wx) * wy * mean_loss; e[(size_t)(y + 1) * ex + x + 1] += wx * wy * mean_loss;
+        }
 
         // depth supervision (:1848-1856): the depth map at the ray's pixel, along the unnormalised ray; views without a map give -1 = no term
         const float target_depth = length3(ld3(rays + (size_t)i * 6 + 3)) * ((cfg->depth_supervision_lambda > 0.0f && m->depth) ? read_depth(m, uv) : -1.0f);
@@ -704,7 +759,7 @@ extern "C" void ref_compute_loss(uint32_t n_rays, const RefAabb* aabb, uint32_t 
             go[0] = f2h(g0); go[1] = f2h(g1); go[2] = f2h(g2); go[3] = f2h(g3);
         }
         if (cfg->exposure_gradient) {   // :1969-1983 (assumes a symmetric loss; uv_pdf = 1 without the error-map CDFs)
-            V3 dgt = v3(-lg.grad.x, -lg.grad.y, -lg.grad.z);
+            V3 dgt = v3(-lg.grad.x / uv_pdf, -lg.grad.y / uv_pdf, -lg.grad.z / uv_pdf);
             if (!cfg->linear_colors) dgt = v3(dgt.x / srgb_to_linear_derivative(target.x), dgt.y / srgb_to_linear_derivative(target.y), dgt.z / srgb_to_linear_derivative(target.z));
             cfg->exposure_gradient[img * 3 + 0] += loss_scale * dgt.x * es.x * 0.6931471805599453f;
             cfg->exposure_gradient[img * 3 + 1] += loss_scale * dgt.y * es.y * 0.6931471805599453f;
@@ -716,6 +771,9 @@ extern "C" void ref_compute_loss(uint32_t n_rays, const RefAabb* aabb, uint32_t 
 
 // compute_cam_gradient_train_nerf (testbed_nerf.cu:2014-2123), extrinsics part (no distortion map, no focal-length gradient, uv_pdf = 1):
 // numsteps are the compacted (count, base) pairs, coords / coords_gradient the compacted batch [*][7]
+static uint64_t g_cam_seed = 0, g_cam_skip = 0; static const RefImage* g_cam_images = nullptr; static int g_cam_snap = 0;
+// the rng stream and views of the step, for the pixel pdf of each ray when the error-map CDFs are in use (:2083-2086)
+extern "C" void ref_set_cam_gradient_rng(uint64_t seed, uint64_t skip, const RefImage* images, int snap) { g_cam_seed = seed; g_cam_skip = skip; g_cam_images = images; g_cam_snap = snap; }
 extern "C" void ref_compute_cam_gradient(uint32_t n_rays, const RefAabb* aabb, uint32_t n_images, uint32_t rays_counter, const uint32_t* ray_indices,
                                          const float* rays, const uint32_t* numsteps, const float* coords, const float* coords_gradient,
                                          float* cam_pos_gradient, float* cam_rot_gradient) {
@@ -724,6 +782,12 @@ extern "C" void ref_compute_cam_gradient(uint32_t n_rays, const RefAabb* aabb, u
         const uint32_t n = numsteps[i * 2], base = numsteps[i * 2 + 1];
         if (n == 0) continue;
         const uint32_t img = image_idx(g_ray_offset + ray_indices[i], n_global, n_images);
+        float uv_pdf = 1.0f;
+        if (g_cdf_x_cond_y && g_cam_images) {
+            RefPcg32 rng; ref_pcg32_seed(&rng, g_cam_seed, 1); ref_pcg32_advance(&rng, (int64_t)g_cam_skip);
+            ref_pcg32_advance(&rng, (int64_t)((uint64_t)(g_ray_offset + ray_indices[i]) * REF_N_MAX_RANDOM_SAMPLES_PER_RAY));
+            float uv[2]; random_image_pos_training(&rng, g_cam_images[img].res, g_cam_snap, uv, img, &uv_pdf);
+        }
         const V3 ray_o = ld3(rays + (size_t)i * 6), ray_d = normalize3(ld3(rays + (size_t)i * 6 + 3));
         V3 go = v3(0, 0, 0), gd = v3(0, 0, 0);
         for (uint32_t j = 0; j < n; ++j) {
@@ -736,13 +800,39 @@ extern "C" void ref_compute_cam_gradient(uint32_t n_rays, const RefAabb* aabb, u
             const V3 dir_gradient = v3(g[4] * 0.5f, g[5] * 0.5f, g[6] * 0.5f);                                       // warp_direction_derivative
             gd = gd + t * pos_gradient + dir_gradient;
         }
-        if (cam_pos_gradient) { cam_pos_gradient[img * 3] += go.x; cam_pos_gradient[img * 3 + 1] += go.y; cam_pos_gradient[img * 3 + 2] += go.z; }
+        if (cam_pos_gradient) { cam_pos_gradient[img * 3] += go.x / uv_pdf; cam_pos_gradient[img * 3 + 1] += go.y / uv_pdf; cam_pos_gradient[img * 3 + 2] += go.z / uv_pdf; }
         if (cam_rot_gradient) {
-            cam_rot_gradient[img * 3] += ray_d.y * gd.z - ray_d.z * gd.y;
-            cam_rot_gradient[img * 3 + 1] += ray_d.z * gd.x - ray_d.x * gd.z;
-            cam_rot_gradient[img * 3 + 2] += ray_d.x * gd.y - ray_d.y * gd.x;
+            cam_rot_gradient[img * 3] += (ray_d.y * gd.z - ray_d.z * gd.y) / uv_pdf;
+            cam_rot_gradient[img * 3 + 1] += (ray_d.z * gd.x - ray_d.x * gd.z) / uv_pdf;
+            cam_rot_gradient[img * 3 + 2] += (ray_d.x * gd.y - ray_d.y * gd.x) / uv_pdf;
         }
     }
+}
+
+// construct_cdf_2d + construct_cdf_1d (testbed_nerf.cu:2354-2409) and the host-side view CDF (:3729-3743)
+extern "C" void ref_construct_error_cdfs(uint32_t n_images, uint32_t height, uint32_t width, const float* data, float* cdf_x_cond_y, float* cdf_y, float* cdf_img) {
+    const float MIN_PDF = 0.01f, MIN_PMF = 0.1f;
+    for (uint32_t img = 0; img < n_images; ++img) {
+        for (uint32_t y = 0; y < height; ++y) {
+            const size_t off = ((size_t)img * height + y) * width;
+            float cum = 0;
+            for (uint32_t x = 0; x < width; ++x) { cum += data[off + x] + 1e-10f; cdf_x_cond_y[off + x] = cum; }
+            cdf_y[(size_t)img * height + y] = cum;
+            float norm = 1.0f / cum;
+            for (uint32_t x = 0; x < width; ++x) cdf_x_cond_y[off + x] = (1.0f - MIN_PDF) * cdf_x_cond_y[off + x] * norm + MIN_PDF * (float)(x + 1) / (float)width;
+        }
+        float* c = cdf_y + (size_t)img * height;
+        float cum = 0;
+        for (uint32_t y = 0; y < height; ++y) { cum += c[y]; c[y] = cum; }
+        cdf_img[img] = cum;
+        float norm = 1.0f / cum;
+        for (uint32_t y = 0; y < height; ++y) c[y] = (1.0f - MIN_PDF) * c[y] * norm + MIN_PDF * (float)(y + 1) / (float)height;
+    }
+    float cum = 0;
+    std::vector<float> c(n_images);
+    for (uint32_t i = 0; i < n_images; ++i) { cum += cdf_img[i]; c[i] = cum; }
+    float norm = 1.0f / cum;
+    for (uint32_t i = 0; i < n_images; ++i) cdf_img[i] = (1.0f - MIN_PMF) * c[i] * norm + MIN_PMF * (float)(i + 1) / (float)n_images;
 }
 
 // fill_rollover_and_rescale / fill_rollover (tcnn common_device; recalled — unpinned): entries [n_input, n_target)

@@ -92,6 +92,12 @@ void ref_generate_training_samples(uint32_t n_rays, const RefAabb* aabb, uint32_
                                    const uint8_t* bitfield, uint32_t max_mip, int snap_to_pixel_centers,
                                    float cone_angle_constant, RefSamplerOut* out);
 
+// Error-map importance sampling (testbed.h:733-738): process-wide state for ref_generate_training_samples / ref_compute_loss / ref_compute_cam_gradient.
+// Non-NULL CDFs steer the pixel (cdf_x_cond_y + cdf_y) and / or the view (cdf_img) of every ray; a non-NULL error_map receives the rays' mean losses.
+void ref_set_error_map(const float* cdf_x_cond_y, const float* cdf_y, const float* cdf_img, int cdf_w, int cdf_h, float* error_map, int map_w, int map_h);
+void ref_set_cam_gradient_rng(uint64_t seed, uint64_t skip, const RefImage* images, int snap);
+// construct_cdf_2d + construct_cdf_1d + the host-side view CDF (testbed_nerf.cu:2354-2409,3729-3743)
+void ref_construct_error_cdfs(uint32_t n_images, uint32_t height, uint32_t width, const float* error_map, float* cdf_x_cond_y, float* cdf_y, float* cdf_img);
 // max_level_rand_training (testbed_nerf.cu:1438,1652-1657,1775,1915-1917): a process-wide switch for the two functions around this line; the
 // level cut-offs go to max_level [max_samples] / max_level_compacted [max_compacted] when the pointers are not NULL
 void ref_set_max_level_rand(int on, float* max_level, float* max_level_compacted);

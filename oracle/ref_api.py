@@ -334,6 +334,27 @@ def compute_loss(n_rays, aabb, seed, skip, max_compacted, rays_counter, cfg, ima
     return r
 
 
+def set_error_map(cdf_x_cond_y=None, cdf_y=None, cdf_img=None, cdf_res=(0, 0), error_map=None, map_res=(0, 0)):
+    """error-map importance sampling state of the sampler / loss / camera-gradient functions; call with no arguments to clear it"""
+    fn = lib().ref_set_error_map; fn.argtypes = [vp, vp, vp, C.c_int, C.c_int, vp, C.c_int, C.c_int]; fn.restype = None
+    q = lambda a: None if a is None else P(a)
+    fn(q(cdf_x_cond_y), q(cdf_y), q(cdf_img), int(cdf_res[0]), int(cdf_res[1]), q(error_map), int(map_res[0]), int(map_res[1]))
+
+
+def set_cam_gradient_rng(seed, skip, images, snap):
+    fn = lib().ref_set_cam_gradient_rng; fn.argtypes = [u64, u64, vp, C.c_int]; fn.restype = None
+    fn(seed, skip, C.cast(images, vp) if images is not None else None, int(snap))
+
+
+def construct_error_cdfs(error_map, n_images, height, width):
+    """-> (cdf_x_cond_y [n, h, w], cdf_y [n, h], cdf_img [n]) as Testbed::train_nerf builds them"""
+    e = np.ascontiguousarray(error_map, np.float32)
+    cxy = np.zeros((n_images, height, width), np.float32); cy = np.zeros((n_images, height), np.float32); cimg = np.zeros(n_images, np.float32)
+    fn = lib().ref_construct_error_cdfs; fn.argtypes = [u32, u32, u32, vp, vp, vp, vp]; fn.restype = None
+    fn(n_images, height, width, P(e), P(cxy), P(cy), P(cimg))
+    return cxy, cy, cimg
+
+
 def rotmat(v):
     """rotmat(vec3) (common_device.cuh:715-722) -> 3 x 3 (rows)"""
     v = np.ascontiguousarray(v, np.float32); m = np.zeros(9, np.float32)
