@@ -71,7 +71,7 @@ static Json lens_json(const ImageMeta& m) {   // to_json(Lens) (json_binding.h:1
 }
 
 // to_json(NerfDataset) (json_binding.h:224-251): poses and intrinsics of the training views, no pixels
-static Json dataset_json(const std::vector<ImageMeta>& metas, const Aabb& render_aabb, int aabb_scale, bool is_hdr, float scale, const float* offset) {
+static Json dataset_json(const std::vector<ImageMeta>& metas, const Aabb& render_aabb, int aabb_scale, bool is_hdr, float scale, const float* offset, const float* up) {
     Json j; j.type = Json::Object;
     j["n_images"] = Json::integer((int64_t)metas.size());
     Json paths, md, xf; paths.type = md.type = xf.type = Json::Array;
@@ -90,10 +90,10 @@ static Json dataset_json(const std::vector<ImageMeta>& metas, const Aabb& render
     }
     j["paths"] = paths; j["metadata"] = md; j["xforms"] = xf;
     j["render_aabb"] = aabb_json(render_aabb);
-    const float eye[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}, up[3] = {0, 1, 0};
+    const float eye[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
     Json r2l; r2l.type = Json::Array; for (int r = 0; r < 3; ++r) r2l.arr.push_back(vec_json(eye + 3 * r, 3));
     j["render_aabb_to_local"] = r2l;
-    j["up"] = vec_json(up, 3); j["offset"] = vec_json(offset, 3);          // the loaded dataset's scale / offset (nerf_loader.cu:388-393); up: loader default
+    j["up"] = vec_json(up, 3); j["offset"] = vec_json(offset, 3);          // the loaded dataset's scale / offset (nerf_loader.cu:388-393) and up vector (what load_nerf_post copied into the testbed's)
     Json er; er.type = Json::Array; er.arr.push_back(Json::integer(0)); er.arr.push_back(Json::integer(0));
     j["envmap_resolution"] = er;
     j["scale"] = Json::number(scale);
@@ -156,7 +156,7 @@ void Testbed::save_snapshot(cudaStream_t s, const std::string& path, bool includ
         // applied again by update_transforms when the snapshot is loaded (testbed.cu:5010-5013)
         std::vector<ImageMeta> given = m_host_metas;
         for (size_t i = 0; i < given.size() && i < m_base_xforms.size(); ++i) { memcpy(given[i].xform, m_base_xforms[i].data(), 48); memcpy(given[i].xform_end, m_base_xforms[i].data() + 12, 48); }
-        nerf["dataset"] = dataset_json(given, render_aabb, m_aabb_scale, !m_all_images_u8, m_ds_scale, m_ds_offset);
+        nerf["dataset"] = dataset_json(given, render_aabb, m_aabb_scale, !m_all_images_u8, m_ds_scale, m_ds_offset, m_dataset_up);
         const auto opt_json = [](const std::vector<VecAdam>& v, float lr) {   // AdamOptimizer<vec3> / RotationAdamOptimizer::to_json (adam_optimizer.h:177-186,265-274)
             Json a; a.type = Json::Array;
             for (const VecAdam& o : v) {
@@ -299,6 +299,7 @@ void Testbed::load_snapshot(cudaStream_t s, const std::string& path) {
             aabb_scale = (int)d.value("aabb_scale", (double)aabb_scale);
             m_ds_scale = (float)d.value("scale", (double)m_ds_scale);
             if (d.contains("offset") && d.at("offset").arr.size() == 3) for (int k = 0; k < 3; ++k) m_ds_offset[k] = (float)d.at("offset").arr[k].num;
+            if (d.contains("up") && d.at("up").arr.size() == 3) for (int k = 0; k < 3; ++k) m_dataset_up[k] = (float)d.at("up").arr[k].num;
         }
         load_nerf_post(s, aabb_scale);
         m_rays_per_batch = (uint32_t)nerf.at("rgb").at("rays_per_batch").num;

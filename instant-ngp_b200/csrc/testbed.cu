@@ -1196,7 +1196,7 @@ void Testbed::apply_dataset_view_hints(bool has_render_aabb, const float* ra, co
     if (has_render_aabb) {   // m_render_aabb = dataset.render_aabb.intersection(m_aabb)
         for (int k = 0; k < 3; ++k) { render_aabb.min[k] = std::max(ra[k], aabb.min[k]); render_aabb.max[k] = std::min(ra[3 + k], aabb.max[k]); }
     }
-    for (int k = 0; k < 3; ++k) up_dir[k] = up3[k];
+    for (int k = 0; k < 3; ++k) { up_dir[k] = up3[k]; m_dataset_up[k] = up3[k]; }
 }
 
 void Testbed::render_frame(cudaStream_t s, int w, int h, int spp, bool to_srgb, int y0, int y1, float* rgba_out, bool out_is_device) {

@@ -233,6 +233,7 @@ private:
     void update_error_map_cdfs(cudaStream_t s);
     DeviceBuffer m_max_level, m_max_level_compacted;        // per-sample level cut-offs (max_level_rand_training)
     size_t m_grid_elements = 0;                             // cells of the occupancy grid as allocated (128^3 x cascades in use)
+    float m_dataset_up[3] = {0.f, 1.f, 0.f};                // NerfDataset::up (nerf_loader.h:88) of the loaded data set
     float m_ds_scale = 0.33f, m_ds_offset[3] = {0.5f, 0.5f, 0.5f};   // NerfDataset::scale / offset (nerf_loader.h:29, nerf_loader.cu:392-393)
     // NerfCounters (testbed.h:433-447)
     uint32_t m_rays_per_batch = 1u << 12, m_n_rays_total = 0, m_measured = 0, m_measured_before = 0;
