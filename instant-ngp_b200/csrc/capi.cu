@@ -569,7 +569,7 @@ int ngp_testbed_debug_buffer(ngp_testbed_t t, const char* name, void** ptr, uint
     X(image_snap_to_pixel_centers, bool) X(image_linear_colors, bool) X(image_random_mode, int) X(sampler_lanes_per_ray, uint32_t) X(prefetch_rays, bool) X(prefetch_hits, uint32_t) X(dp_sharded_optimizer, bool) X(device_control_law, bool) \
     X(exposure, float) X(zoom, float) X(scale, float) X(ground_truth_alpha, float) X(render_near_distance, float) X(fov_axis, int) X(training_view, int)                      \
     X(color_space, int) X(tonemap_curve, int) X(render_mode, int) X(render_ground_truth, bool) X(render_with_lens_distortion, bool) X(render_row_stride, int) X(walk_ahead, bool) X(walk_ahead_hits, uint32_t) X(walk_ahead_misses, uint32_t) \
-    X(optimize_exposure, bool) X(exposure_l2_reg, float) X(n_steps_between_cam_updates, uint32_t) X(max_level_rand_training, bool) X(depth_supervision_lambda, float) X(depth_loss_type, int) X(optimize_extrinsics, bool) X(extrinsic_l2_reg, float) X(extrinsic_learning_rate, float) \
+    X(optimize_exposure, bool) X(exposure_l2_reg, float) X(n_steps_between_cam_updates, uint32_t) X(max_level_rand_training, bool) X(depth_supervision_lambda, float) X(depth_loss_type, int) X(optimize_extrinsics, bool) X(optimize_distortion, bool) X(extrinsic_l2_reg, float) X(extrinsic_learning_rate, float) \
     X(sample_focal_plane_proportional_to_error, bool) X(sample_image_proportional_to_error, bool) X(n_steps_between_error_map_updates, uint32_t)
 
 int ngp_testbed_set_option(ngp_testbed_t t, const char* name, double value) {

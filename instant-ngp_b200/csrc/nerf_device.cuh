@@ -266,10 +266,23 @@ NGP_HD void opencv_undistort(const float* params, float* u, float* v) {
     *u = x[0]; *v = x[1];
 }
 // uv -> unnormalised ray; default args of uv_to_ray (no foveation / parallax / aperture / near plane)
+// The trainable distortion map (Testbed::m_distortion, TrainableBuffer<2, 2, float>; testbed.cu:4066-4077): a res[0] x res[1] lattice of 2-D offsets
+// that uv_to_ray adds to the ray direction's x, y on the image plane, looked up bilinearly at the ray's uv (Buffer2DView::at_lerp, common.h:384-400)
+struct DistortionMap { const float* data; int res[2]; };
+NGP_HD void distortion_at_lerp(const DistortionMap& m, float u, float v, float* out2) {
+    const float xf = (float)m.res[0] * u, yf = (float)m.res[1] * v;
+    const int x = (int)xf, y = (int)yf;
+    const float wx = xf - (float)x, wy = yf - (float)y;
+    const int x0 = clampi(x, 0, m.res[0] - 1), x1 = clampi(x + 1, 0, m.res[0] - 1), y0 = clampi(y, 0, m.res[1] - 1), y1 = clampi(y + 1, 0, m.res[1] - 1);
+    const float* a = m.data + 2 * ((size_t)x0 + (size_t)y0 * m.res[0]); const float* b = m.data + 2 * ((size_t)x1 + (size_t)y0 * m.res[0]);
+    const float* c = m.data + 2 * ((size_t)x0 + (size_t)y1 * m.res[0]); const float* d = m.data + 2 * ((size_t)x1 + (size_t)y1 * m.res[0]);
+    for (int k = 0; k < 2; ++k) out2[k] = (1 - wx) * (1 - wy) * a[k] + wx * (1 - wy) * b[k] + (1 - wx) * wy * c[k] + wx * wy * d[k];
+}
 NGP_HD void uv_to_ray(const float* xform, const int* res, const float* focal, const float* principal, int lens_mode, const float* lens_params,
-                      float u, float v, V3& o, V3& d) {
+                      float u, float v, V3& o, V3& d, const DistortionMap* distortion = nullptr) {
     V3 dir = {(u - principal[0]) * (float)res[0] / focal[0], (v - principal[1]) * (float)res[1] / focal[1], 1.0f};
     if (lens_mode == LENS_OPENCV) opencv_undistort(lens_params, &dir.x, &dir.y);
+    if (distortion && distortion->data) { float off[2]; distortion_at_lerp(*distortion, u, v, off); dir.x += off[0]; dir.y += off[1]; }   // common_device.cuh:491-493
     d = mat3_mul(xform, dir);
     o = v3(xform[9], xform[10], xform[11]);
 }

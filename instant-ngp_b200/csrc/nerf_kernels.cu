@@ -497,7 +497,7 @@ __global__ void __launch_bounds__(SCAN_BLOCK) sampler_count_kernel(uint32_t n_ra
             if (b.max_level_rand) rng.advance(1);             // :1438 the ray's level cut-off (nerf_fill_max_level hands it to the samples)
             const float motionblur_time = rng.next_float();   // :1440
             float xf[12]; xform_given_rolling_shutter(m.xform, m.xform_end, m.rolling_shutter, uv[0], uv[1], motionblur_time, xf);   // :1447-1451
-            V3 o, du; uv_to_ray(xf, m.res, m.focal_length, m.principal_point, m.lens_mode, m.lens_params, uv[0], uv[1], o, du);
+            V3 o, du; uv_to_ray(xf, m.res, m.focal_length, m.principal_point, m.lens_mode, m.lens_params, uv[0], uv[1], o, du, &b.distortion);
             if (du.x == 0.f && du.y == 0.f && du.z == 0.f) { o = v3(xf[9], xf[10], xf[11]); du = v3(xf[6], xf[7], xf[8]); }
             const V3 d = normalize3(du);
             float tmin, tmax; aabb_ray_intersect(aabb, o, d, tmin, tmax);
@@ -744,7 +744,7 @@ __global__ void __launch_bounds__(128) sampler_classify_kernel(uint32_t n_rays, 
             if (b.max_level_rand) rng.advance(1);             // :1438 the ray's level cut-off (nerf_fill_max_level hands it to the samples)
             const float motionblur_time = rng.next_float();   // :1440
             float xf[12]; xform_given_rolling_shutter(m.xform, m.xform_end, m.rolling_shutter, uv[0], uv[1], motionblur_time, xf);   // :1447-1451
-            V3 o, du; uv_to_ray(xf, m.res, m.focal_length, m.principal_point, m.lens_mode, m.lens_params, uv[0], uv[1], o, du);
+            V3 o, du; uv_to_ray(xf, m.res, m.focal_length, m.principal_point, m.lens_mode, m.lens_params, uv[0], uv[1], o, du, &b.distortion);
             if (du.x == 0.f && du.y == 0.f && du.z == 0.f) { o = v3(xf[9], xf[10], xf[11]); du = v3(xf[6], xf[7], xf[8]); }
             const V3 d = normalize3(du);
             float tmin, tmax; aabb_ray_intersect(aabb, o, d, tmin, tmax);
@@ -1417,7 +1417,7 @@ void nerf_compute_loss(cudaStream_t s, uint32_t n_rays, Aabb aabb, uint32_t n_ra
 
 __global__ void cam_gradient_kernel(Aabb aabb, Pcg32 rng, bool snap, const ImageMeta* __restrict__ metas, uint32_t n_images, uint32_t ray_offset, uint32_t n_rays_global, SamplerBuffers sb,
                                     const float* __restrict__ coords, const float* __restrict__ coords_gradient, float* __restrict__ cam_pos_gradient,
-                                    float* __restrict__ cam_rot_gradient) {
+                                    float* __restrict__ cam_rot_gradient, float* __restrict__ distortion_gradient, float* __restrict__ distortion_gradient_weight) {
     const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x;
     if (i >= sb.counters[0]) return;
     const uint32_t numsteps = sb.numsteps[i * 2 + 0];
@@ -1425,10 +1425,10 @@ __global__ void cam_gradient_kernel(Aabb aabb, Pcg32 rng, bool snap, const Image
     const uint32_t base = sb.numsteps[i * 2 + 1];
     const uint32_t ig = ray_offset + sb.ray_indices[i];
     const uint32_t img = image_idx(ig, n_rays_global, n_images, sb.cdf.cdf_img);
-    float uv_pdf = 1.0f;
-    if (sb.cdf.cdf_x_cond_y) {   // the pixel pdf of the ray, from the replayed rng stream (:2083-2086)
+    float uv_pdf = 1.0f; float uv[2] = {0.f, 0.f};
+    if (sb.cdf.cdf_x_cond_y || distortion_gradient) {   // the pixel (and its pdf) of the ray, from the replayed rng stream (:2083-2086)
         rng.advance((int64_t)((uint64_t)ig * N_MAX_RANDOM_SAMPLES_PER_RAY));
-        float uv[2]; random_image_pos_training(rng, metas[img].res, snap, uv, &sb.cdf, img, &uv_pdf);
+        random_image_pos_training(rng, metas[img].res, snap, uv, &sb.cdf, img, &uv_pdf);
     }
     const V3 ray_o = ld3(sb.rays + (size_t)i * 6), ray_d = normalize3(ld3(sb.rays + (size_t)i * 6 + 3));
     const V3 wpd = v3(1.0f / (aabb.max[0] - aabb.min[0]), 1.0f / (aabb.max[1] - aabb.min[1]), 1.0f / (aabb.max[2] - aabb.min[2]));   // warp_position_derivative (:397-405)
@@ -1442,6 +1442,30 @@ __global__ void cam_gradient_kernel(Aabb aabb, Pcg32 rng, bool snap, const Image
         const V3 dir_gradient = v3(g[4] * 0.5f, g[5] * 0.5f, g[6] * 0.5f);   // warp_direction_derivative (:415-417)
         gd = gd + t * pos_gradient + dir_gradient;
     }
+    if (distortion_gradient) {   // :2088-2100
+        // "Projection of the raydir gradient onto the plane normal to raydir, because that's the only degree of motion that the raydir has",
+        // then rotated into the image plane of the view (inverse of the rotation block, by cofactors as glm does) and splatted at the ray's pixel
+        const float dp = gd.x * ray_d.x + gd.y * ray_d.y + gd.z * ray_d.z;
+        const V3 og = gd - dp * ray_d;
+        const float* m = metas[img].xform;
+        const float a = m[0], b = m[3], c = m[6], d_ = m[1], e = m[4], f = m[7], g = m[2], h = m[5], k = m[8];
+        const float id = 1.0f / (a * (e * k - f * h) - b * (d_ * k - f * g) + c * (d_ * h - e * g));
+        const float ix = ((e * k - f * h) * og.x + (c * h - b * k) * og.y + (b * f - c * e) * og.z) * id;
+        const float iy = ((f * g - d_ * k) * og.x + (a * k - c * g) * og.y + (c * d_ - a * f) * og.z) * id;
+        const float val[2] = {ix / uv_pdf, iy / uv_pdf};
+        const int rx = sb.distortion.res[0], ry = sb.distortion.res[1];
+        const float xf = (float)rx * uv[0], yf = (float)ry * uv[1];
+        const int tx = (int)xf, ty = (int)yf;
+        const float wx = xf - (float)tx, wy = yf - (float)ty;
+        const float w4[4] = {(1 - wx) * (1 - wy), wx * (1 - wy), (1 - wx) * wy, wx * wy};
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int px = clampi(tx + (q & 1), 0, rx - 1), py = clampi(ty + (q >> 1), 0, ry - 1);
+            const size_t o = 2 * ((size_t)px + (size_t)py * rx);
+            atomicAdd(distortion_gradient + o, val[0] * w4[q]); atomicAdd(distortion_gradient_weight + o, w4[q]);
+            atomicAdd(distortion_gradient + o + 1, val[1] * w4[q]); atomicAdd(distortion_gradient_weight + o + 1, w4[q]);
+        }
+    }
     if (cam_pos_gradient) { atomicAdd(cam_pos_gradient + img * 3, go.x / uv_pdf); atomicAdd(cam_pos_gradient + img * 3 + 1, go.y / uv_pdf); atomicAdd(cam_pos_gradient + img * 3 + 2, go.z / uv_pdf); }
     if (cam_rot_gradient) {                                     // averaged in log space: angle_axis = cross(ray.d, ray_gradient.d) (:2110-2122)
         const V3 aa = v3(ray_d.y * gd.z - ray_d.z * gd.y, ray_d.z * gd.x - ray_d.x * gd.z, ray_d.x * gd.y - ray_d.y * gd.x);
@@ -1450,11 +1474,36 @@ __global__ void cam_gradient_kernel(Aabb aabb, Pcg32 rng, bool snap, const Image
 }
 void nerf_compute_cam_gradient(cudaStream_t s, uint32_t n_rays_bound, Aabb aabb, Pcg32 rng, bool snap_to_pixel_centers, const ImageMeta* metas, uint32_t n_images,
                                uint32_t ray_offset, uint32_t n_rays_global, const SamplerBuffers& sb, const float* coords_compacted, const float* coords_gradient,
-                               float* cam_pos_gradient, float* cam_rot_gradient) {
+                               float* cam_pos_gradient, float* cam_rot_gradient, float* distortion_gradient, float* distortion_gradient_weight) {
     if (n_rays_bound == 0) return;
     NGP_PROFILE_SCOPE(s, "cam_gradient", n_rays_bound);
     cam_gradient_kernel<<<div_round_up(n_rays_bound, 128), 128, 0, s>>>(aabb, rng, snap_to_pixel_centers, metas, n_images, ray_offset, n_rays_global, sb, coords_compacted,
-                                                                      coords_gradient, cam_pos_gradient, cam_rot_gradient);
+                                                                      coords_gradient, cam_pos_gradient, cam_rot_gradient, distortion_gradient, distortion_gradient_weight);
+    NGP_POST_LAUNCH();
+}
+
+// safe_divide (testbed_nerf.cu:2411-2417) fused with tiny-cuda-nn's Adam step on fp32 parameters that are all non-matrix (a TrainableBuffer has no
+// layers): entries whose gradient is zero are skipped and keep their step count, no L2 term, lr bias-corrected per entry (recalled; unpinned)
+__global__ void distortion_step_kernel(uint32_t n, float* __restrict__ params, float* __restrict__ gradient, const float* __restrict__ weight, float* __restrict__ m1,
+                                       float* __restrict__ m2, uint32_t* __restrict__ steps, float lr, float beta1, float beta2, float epsilon, float loss_scale) {
+    const uint32_t i = threadIdx.x + blockIdx.x * blockDim.x;
+    if (i >= n) return;
+    const float w = weight[i];
+    const float divided = w > 0.0f ? gradient[i] / w : 0.0f;
+    gradient[i] = divided;
+    const float g = divided / loss_scale;
+    if (g == 0.0f) return;
+    const uint32_t step = ++steps[i];
+    const float learning_rate = lr * sqrtf(1.0f - powf(beta2, (float)step)) / (1.0f - powf(beta1, (float)step));
+    const float first = m1[i] = beta1 * m1[i] + (1.0f - beta1) * g;
+    const float second = m2[i] = beta2 * m2[i] + (1.0f - beta2) * g * g;
+    params[i] = params[i] - learning_rate / (sqrtf(second) + epsilon) * first;
+}
+void nerf_distortion_step(cudaStream_t s, uint32_t n_params, float* params, float* gradient, const float* gradient_weight, float* first_moment, float* second_moment,
+                          uint32_t* steps, float learning_rate, float beta1, float beta2, float epsilon, float loss_scale) {
+    if (n_params == 0) return;
+    distortion_step_kernel<<<div_round_up(n_params, 256), 256, 0, s>>>(n_params, params, gradient, gradient_weight, first_moment, second_moment, steps, learning_rate, beta1, beta2,
+                                                                     epsilon, loss_scale);
     NGP_POST_LAUNCH();
 }
 
@@ -1578,7 +1627,7 @@ __global__ void init_rays_kernel(RenderCamera cam, uint32_t sample_index, bool s
     float off[2]; ld_random_pixel_offset(snap ? 0 : sample_index, off);
     const float u = ((float)x + off[0]) / (float)W, v = ((float)y + off[1]) / (float)cam.res[1];
     V3 o, d;
-    uv_to_ray(cam.camera, cam.res, cam.focal_length, cam.screen_center, cam.lens_mode, cam.lens_params, u, v, o, d);
+    uv_to_ray(cam.camera, cam.res, cam.focal_length, cam.screen_center, cam.lens_mode, cam.lens_params, u, v, o, d, &cam.distortion);
     if (near_distance != 0.f) o = ray_at(o, d, near_distance);   // uv_to_ray: origin += dir * near_distance (dir not yet normalised)
     NerfPayload& p = rays.payload[local];
     p.max_weight = 0.0f; p.idx = idx; p.n_steps = 0; p.alive = 0; p.pad = 0;

@@ -62,6 +62,7 @@ struct SamplerBuffers {
     // between the pixel position and the motion-blur time, which shifts everything drawn after it
     uint32_t max_level_rand;
     ErrorMapCdf cdf;            // all null: uniform pixels, views in ray order
+    DistortionMap distortion;   // data null: none (optimize_distortion off and never trained)
 };
 uint32_t nerf_sampler_lanes_per_ray(uint32_t n_rays);
 // max_level of the un-compacted samples (testbed_nerf.cu:1438,1652-1657): ray i's cut-off = 2 * (the random number after its pixel position), written
@@ -113,9 +114,16 @@ void nerf_construct_error_cdfs(cudaStream_t s, uint32_t n_images, uint32_t heigh
 // (coords_gradient [*][7]: position cols 0..2, direction cols 4..6) are summed into dL/d(ray origin) and dL/d(ray direction); the origin part is
 // added to cam_pos_gradient[image], cross(ray direction, direction part) to cam_rot_gradient[image] (angle-axis, log space).  Run behind the
 // backward pass; numsteps are the COMPACTED (count, base) pairs the loss kernel left.
+// distortion_gradient / distortion_gradient_weight (optional, [res[1]][res[0]][2] fp32 each, lattice of sb.distortion): the ray's direction gradient,
+// projected onto the plane normal to the ray and rotated into the view's image plane, splatted bilinearly at the ray's uv together with the splat
+// weights (deposit_image_gradient, common_device.cuh:124-156; testbed_nerf.cu:2088-2100)
 void nerf_compute_cam_gradient(cudaStream_t s, uint32_t n_rays_bound, Aabb aabb, Pcg32 rng, bool snap_to_pixel_centers, const ImageMeta* metas, uint32_t n_images,
                                uint32_t ray_offset, uint32_t n_rays_global, const SamplerBuffers& sb, const float* coords_compacted, const float* coords_gradient,
-                               float* cam_pos_gradient, float* cam_rot_gradient);
+                               float* cam_pos_gradient, float* cam_rot_gradient, float* distortion_gradient = nullptr, float* distortion_gradient_weight = nullptr);
+// the camera update of the distortion map (testbed_nerf.cu:3811-3818): gradient / weight where the weight is positive (safe_divide, :2411-2417), then
+// one step of tiny-cuda-nn's Adam on fp32 parameters that are all "non-matrix" (entries with a zero gradient are skipped, no L2 term; recalled)
+void nerf_distortion_step(cudaStream_t s, uint32_t n_params, float* params, float* gradient, const float* gradient_weight, float* first_moment, float* second_moment,
+                          uint32_t* steps, float learning_rate, float beta1, float beta2, float epsilon, float loss_scale);
 void nerf_compute_loss(cudaStream_t s, uint32_t n_rays, Aabb aabb, uint32_t n_rays_total, Pcg32 rng, uint32_t max_samples_compacted,
                        const LossConfig& cfg, uint32_t n_images, const ImageMeta* metas, const float* mean_density_dev,
                        uint32_t ray_offset, uint32_t n_rays_global, const SamplerBuffers& sb, const LossBuffers& lb);
@@ -141,6 +149,7 @@ struct RenderCamera {
     int y0, y1;     // rows y0, y0 + y_stride, ... < y1 are rendered by this call (tile sharding: a band, or every world-th row); local ray index = x + W*((y - y0) / y_stride)
     int y_stride;
     int lens_mode; float lens_params[4];   // m_nerf.render_lens (render_with_lens_distortion): Perspective or OpenCV
+    DistortionMap distortion;              // the trained distortion map, with render_with_lens_distortion (testbed_nerf.cu:2776-2778); data null: none
 };
 // Loop control of the wavefront tracer lives on the device (the reference reads n_alive back and synchronises every iteration,
 // testbed_nerf.cu:2540-2560): iteration `it` reads ctl[(it - 1) & 1] and its compaction writes ctl[it & 1] plus a copy into host-mapped

@@ -161,7 +161,42 @@ void Testbed::reset_network(bool clear_density_grid) {
         m_image_net->initialize_params(seed, m_trainer->master, 0);
     }
     m_trainer->params_from_master(0);
+    if (m_mode == MODE_TB_NERF) {   // "Create distortion map model" (testbed.cu:4066-4077): zeros, its own optimizer (the main one's config when none is given)
+        m_distortion_res[0] = m_distortion_res[1] = 32;
+        const Json* dopt = &opt;
+        if (m_config.contains("distortion_map")) {
+            const Json& dm = m_config.at("distortion_map");
+            if (dm.contains("resolution") && dm.at("resolution").arr.size() == 2) { m_distortion_res[0] = (int)dm.at("resolution").arr[0].num; m_distortion_res[1] = (int)dm.at("resolution").arr[1].num; }
+            if (dm.contains("optimizer")) dopt = &dm.at("optimizer");
+        }
+        NGP_CHECK(m_distortion_res[0] > 0 && m_distortion_res[1] > 0, "distortion_map: bad resolution");
+        m_distortion_opt = std::make_unique<Optimizer>(*dopt);
+        m_distortion_live = false; ++m_distortion_version;
+    }
     NGP_CUDA_CHECK(cudaDeviceSynchronize());
+}
+
+void Testbed::ensure_distortion_map(cudaStream_t s) {
+    if (m_distortion_live) return;
+    const size_t n = (size_t)m_distortion_res[0] * m_distortion_res[1] * 2;
+    for (DeviceBuffer* b : {&m_distortion_map, &m_distortion_grad, &m_distortion_weight, &m_distortion_m1, &m_distortion_m2})
+        NGP_CUDA_CHECK(cudaMemsetAsync(b->get<float>(n), 0, n * sizeof(float), s));
+    NGP_CUDA_CHECK(cudaMemsetAsync(m_distortion_steps.get<uint32_t>(n), 0, n * sizeof(uint32_t), s));
+    m_distortion_live = true; ++m_distortion_version;
+    m_prefetch_valid = false; m_walk_ahead_valid = false; m_early_prefetch = false;
+}
+
+// the distortion part of the camera update (testbed_nerf.cu:3811-3818): gradients / weights, Trainer::optimizer_step(LOSS_SCALE * n_steps_between_cam_updates)
+void Testbed::distortion_step(cudaStream_t s) {
+    if (m_aux_stream) NGP_CUDA_CHECK(cudaStreamSynchronize(m_aux_stream));   // a sampler in flight reads the map
+    Optimizer& o = *m_distortion_opt;
+    const uint32_t n = (uint32_t)(m_distortion_res[0] * m_distortion_res[1] * 2);
+    nerf_distortion_step(s, n, m_distortion_map.as<float>(), m_distortion_grad.as<float>(), m_distortion_weight.as<float>(), m_distortion_m1.as<float>(),
+                         m_distortion_m2.as<float>(), m_distortion_steps.as<uint32_t>(), o.current_lr, o.beta1, o.beta2, o.epsilon, LOSS_SCALE * (float)n_steps_between_cam_updates);
+    ++o.step_count;
+    if (o.decay_interval > 0 && o.step_count >= o.decay_start && o.step_count < o.decay_end && (o.step_count - o.decay_start) % o.decay_interval == 0) o.current_lr *= o.decay_base;
+    ++m_distortion_version;
+    m_prefetch_valid = false; m_walk_ahead_valid = false; m_early_prefetch = false;
 }
 
 // NerfDataset upload + load_nerf_post (testbed_nerf.cu:3046-3112): aabb, cascades, cone angle
@@ -554,6 +589,7 @@ void Testbed::train_begin(cudaStream_t s, uint32_t batch_size) {
     NGP_CHECK(batch_size >= BATCH_GRANULARITY && batch_size % BATCH_GRANULARITY == 0, "training batch size must be a multiple of 256");
     if (m_mode == MODE_TB_NERF) {
         NGP_CHECK(m_n_images > 0, "Cannot train without training data");
+        if (optimize_distortion) ensure_distortion_map(s);   // before this step's sampler looks at it (a prefetched walk without the map is discarded)
         const uint32_t n_prep_to_skip = std::min(std::max(m_training_step / 16u, 1u), 16u);
         if (m_training_step % n_prep_to_skip == 0) training_prep_nerf(s);
     }
@@ -652,8 +688,10 @@ void Testbed::train_end(cudaStream_t s, uint32_t measured_override, uint32_t mea
     }
     m_n_steps_since_cam_update += 1;
     const bool train_exposure = optimize_exposure && m_cam_exposure_n == m_n_images, train_extrinsics = optimize_extrinsics && m_cam_pos_grad.ptr != nullptr;
-    if ((train_exposure || train_extrinsics) && m_n_steps_since_cam_update >= n_steps_between_cam_updates) {   // :3767-3771
+    const bool train_distortion = optimize_distortion && m_distortion_live;
+    if ((train_exposure || train_extrinsics || train_distortion) && m_n_steps_since_cam_update >= n_steps_between_cam_updates) {   // :3767-3771
         if (train_extrinsics) extrinsics_step(s);   // host-side Adam per view, as in the reference; the new poses are on the device before the next sampler runs
+        if (train_distortion) distortion_step(s);
         if (train_exposure) {
             const float per_camera_loss_scale = (float)m_n_images / LOSS_SCALE / (float)n_steps_between_cam_updates;
             nerf_exposure_step(s, m_n_images, m_cam_exposure_grad.as<float>(), m_cam_exposure.as<float>(), m_cam_exposure_m1.as<float>(), m_cam_exposure_m2.as<float>(),
@@ -705,7 +743,8 @@ Testbed::SamplerKey Testbed::sampler_key(uint32_t n_rays, uint32_t max_inference
     return {m_training_step, n_rays, max_inference, target, m_rank, m_world, sampler_lanes_per_ray, m_dataset_version, m_rng.state, m_rng.inc,
             cone_angle_constant, train_snap_to_pixel_centers, max_level_rand_training,
             // the CDFs the sampler draws from: their version, and which of the two switches use them
-            m_cdf_valid ? (m_cdf_version * 4u + (sample_focal_plane_proportional_to_error ? 1u : 0u) + (sample_image_proportional_to_error ? 2u : 0u)) : 0u};
+            m_cdf_valid ? (m_cdf_version * 4u + (sample_focal_plane_proportional_to_error ? 1u : 0u) + (sample_image_proportional_to_error ? 2u : 0u)) : 0u,
+            m_distortion_live ? m_distortion_version + 1u : 0u};
 }
 
 SamplerBuffers Testbed::sampler_buffers(cudaStream_t s, uint32_t set, uint32_t target, uint32_t n_rays) {
@@ -714,6 +753,7 @@ SamplerBuffers Testbed::sampler_buffers(cudaStream_t s, uint32_t set, uint32_t t
     const uint32_t max_blocks = max_rays / 8 + 1;   // 256 / lanes_per_ray rays per block, lanes_per_ray <= 32
     SamplerBuffers sb{};
     sb.max_level_rand = max_level_rand_training ? 1u : 0u;
+    sb.distortion = distortion_view();
     if (m_cdf_valid) {   // :3963-3967,4027-4031: each switch hands its CDFs to the sampler and to every kernel that replays the ray's rng stream
         if (sample_focal_plane_proportional_to_error) { sb.cdf.cdf_x_cond_y = m_cdf_x_cond_y.as<float>(); sb.cdf.cdf_y = m_cdf_y.as<float>(); }
         if (sample_image_proportional_to_error) sb.cdf.cdf_img = m_cdf_img.as<float>();
@@ -928,12 +968,18 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
         lb.error_map = m_error_map.as<float>(); lb.error_map_res[0] = m_error_map_res[0]; lb.error_map_res[1] = m_error_map_res[1];
     } else m_error_map_live = false;
     float* dL_dcoords = nullptr;
-    if (optimize_extrinsics) {   // train_camera (:4071-4073): the backward pass also returns dL/d(coords); per-view accumulators cleared at the start of a window (:3641-3644)
-        NGP_CHECK(!m_comm && m_world == 1, "optimize_extrinsics is not available in data-parallel training");
+    if (optimize_extrinsics || optimize_distortion) {   // train_camera (:4071-4073): the backward pass also returns dL/d(coords); accumulators cleared at the start of a window (:3641-3647)
+        NGP_CHECK(!m_comm && m_world == 1, "optimize_extrinsics / optimize_distortion are not available in data-parallel training");
         dL_dcoords = m_coords_gradient.get<float>((size_t)target * 7);
+    }
+    if (optimize_extrinsics) {
         const bool fresh = m_cam_pos_grad.ptr == nullptr;
         float* gp = m_cam_pos_grad.get<float>((size_t)m_n_images * 3); float* gr = m_cam_rot_grad.get<float>((size_t)m_n_images * 3);
         if (fresh || m_n_steps_since_cam_update == 0) { NGP_CUDA_CHECK(cudaMemsetAsync(gp, 0, (size_t)m_n_images * 12, s)); NGP_CUDA_CHECK(cudaMemsetAsync(gr, 0, (size_t)m_n_images * 12, s)); }
+    }
+    if (optimize_distortion && m_n_steps_since_cam_update == 0) {   // (the map itself was created before the sampler ran: train_begin)
+        const size_t n = (size_t)m_distortion_res[0] * m_distortion_res[1] * 2;
+        NGP_CUDA_CHECK(cudaMemsetAsync(m_distortion_grad.as<float>(), 0, n * 4, s)); NGP_CUDA_CHECK(cudaMemsetAsync(m_distortion_weight.as<float>(), 0, n * 4, s));
     }
     lb.enc_in = m_nerf_net->last_inference_encoding();   // written by inference() just above
     if (m_copy_pending) { NGP_CUDA_CHECK(cudaStreamWaitEvent(s, m_ev_copy_done, 0)); m_copy_pending = false; }   // uploaded view(s), see set_training_image
@@ -947,7 +993,7 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
         const bool next_refreshes_grid = next_step % skip == 0;
         const uint32_t rb = std::min<uint32_t>(1u << 18, (uint32_t)next_multiple((uint64_t)R + R / 2 + BATCH_GRANULARITY, BATCH_GRANULARITY));
         const uint32_t lanes = sampler_lanes_per_ray ? sampler_lanes_per_ray : nerf_sampler_lanes_per_ray(rb);
-        if (device_control_law && prefetch_rays && m_all_images_u8 && !m_comm && m_world == 1 && !next_refreshes_grid && lanes != 1 && !m_walk_ahead_valid && !optimize_extrinsics && !error_sampling) {
+        if (device_control_law && prefetch_rays && m_all_images_u8 && !m_comm && m_world == 1 && !next_refreshes_grid && lanes != 1 && !m_walk_ahead_valid && !optimize_extrinsics && !optimize_distortion && !error_sampling) {
             early_rays_bound = rb;
             early_samples_bound = std::min<uint32_t>(max_samples, (uint32_t)next_multiple((uint64_t)max_inference + max_inference / 2 + BATCH_GRANULARITY, BATCH_GRANULARITY));
             StepParams* sp = m_step_params[next_step % N_SETS].get<StepParams>(1);
@@ -992,7 +1038,8 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
                                              nullptr, dL_dcoords);
         if (dL_dcoords)   // :4098-4124
             nerf_compute_cam_gradient(s, R, aabb, m_rng, train_snap_to_pixel_centers, m_metas.as<ImageMeta>(), m_n_images, ray_offset, n_rays_global, sb, lb.coords_compacted, dL_dcoords,
-                                      m_cam_pos_grad.as<float>(), m_cam_rot_grad.as<float>());
+                                      optimize_extrinsics ? m_cam_pos_grad.as<float>() : nullptr, optimize_extrinsics ? m_cam_rot_grad.as<float>() : nullptr,
+                                      optimize_distortion ? m_distortion_grad.as<float>() : nullptr, optimize_distortion ? m_distortion_weight.as<float>() : nullptr);
     }
     m_trainer->grid_grads_clean = false;
     m_nerf_net->max_level_gpu = nullptr;   // :4130
@@ -1220,7 +1267,7 @@ void Testbed::render_frame(cudaStream_t s, int w, int h, int spp, bool to_srgb, 
         cam.screen_center[k] = (0.5f - screen_center[k]) * zoom + 0.5f;                    // render_screen_center
     }
     memcpy(cam.camera, camera, sizeof(camera));
-    if (render_with_lens_distortion) { cam.lens_mode = render_lens_mode; memcpy(cam.lens_params, render_lens_params, 16); }
+    if (render_with_lens_distortion) { cam.lens_mode = render_lens_mode; memcpy(cam.lens_params, render_lens_params, 16); cam.distortion = distortion_view(); }   // testbed_nerf.cu:2776-2779
     const int out_cs = to_srgb ? CS_SRGB : CS_LINEAR;
     NGP_CUDA_CHECK(cudaMemsetAsync(accum, 0, (size_t)n_pixels * 16, s));
     for (int sample = 0; sample < spp; ++sample) {
@@ -1256,7 +1303,7 @@ void Testbed::debug_buffer(const std::string& name, void** ptr, uint64_t* bytes)
                        {"mlp_out", &m_mlp_out}, {"dloss", &m_dloss}, {"coords_compacted", &m_coords_compacted}, {"loss", &m_loss},
                        {"grid_pos", &m_grid_pos}, {"grid_idx", &m_grid_idx}, {"grid_out", &m_grid_out}, {"density_grid_tmp", &m_density_grid_tmp},
                        {"mean_density", &m_mean}, {"cam_exposure", &m_cam_exposure}, {"cam_exposure_gradient", &m_cam_exposure_grad}, {"numsteps_all", &m_numsteps_all[k]}, {"image_pos", &m_img_pos}, {"image_target", &m_img_target},
-                       {"image_out", &m_img_out}, {"image_dl", &m_img_dl}, {"image", &m_image}, {"max_level", &m_max_level}, {"max_level_compacted", &m_max_level_compacted}, {"error_map", &m_error_map}, {"cdf_x_cond_y", &m_cdf_x_cond_y}, {"cdf_y", &m_cdf_y}, {"cdf_img", &m_cdf_img}, {"cam_pos_gradient", &m_cam_pos_grad}, {"cam_rot_gradient", &m_cam_rot_grad}, {"coords_gradient", &m_coords_gradient}, {"sdf_positions", &m_sdf_pos}, {"sdf_distances", &m_sdf_dist}};
+                       {"image_out", &m_img_out}, {"image_dl", &m_img_dl}, {"image", &m_image}, {"max_level", &m_max_level}, {"max_level_compacted", &m_max_level_compacted}, {"distortion_map", &m_distortion_map}, {"distortion_gradient", &m_distortion_grad}, {"distortion_gradient_weight", &m_distortion_weight}, {"error_map", &m_error_map}, {"cdf_x_cond_y", &m_cdf_x_cond_y}, {"cdf_y", &m_cdf_y}, {"cdf_img", &m_cdf_img}, {"cam_pos_gradient", &m_cam_pos_grad}, {"cam_rot_gradient", &m_cam_rot_grad}, {"coords_gradient", &m_coords_gradient}, {"sdf_positions", &m_sdf_pos}, {"sdf_distances", &m_sdf_dist}};
     for (const E& e : table) if (name == e.n) { *ptr = e.b->ptr; *bytes = e.b->bytes; return; }
     throw Error("debug_buffer: unknown buffer '" + name + "'");
 }

@@ -51,6 +51,10 @@ public:
     // position and rotation offsets trained from the network's input gradients (testbed_nerf.cu:2014-2123,3780-3808,2984-3023)
     struct VecAdam { uint32_t iter = 0; float m1[3] = {0, 0, 0}, m2[3] = {0, 0, 0}, var[3] = {0, 0, 0}; };   // state of one vec3 optimiser
     bool optimize_extrinsics = false; float extrinsic_l2_reg = 1e-4f, extrinsic_learning_rate = 1e-3f;
+    // nerf.training.optimize_distortion (testbed.h:723; python_api.cu:623): a lattice of 2-D image-plane offsets shared by all views (config
+    // "distortion_map": resolution 32 x 32 and its own optimizer, testbed.cu:4066-4077), added to every ray direction and trained from the ray-direction
+    // gradients at the camera-update cadence (testbed_nerf.cu:2088-2100,3811-3818)
+    bool optimize_distortion = false;
     // nerf.training.get_camera_extrinsics(frame_idx, convert_to_ngp) (python_api.cu:594-603; testbed_nerf.cu:2925-2932): the view's pose as trained
     void get_camera_extrinsics(int frame_idx, bool convert_to_ngp, float* out12) const;
     // NerfDataset::set_training_image's depth half (nerf_loader.cu:943-959): host depth map of view frame_idx (depth_type 0: uint16, 1: float32), stored
@@ -199,10 +203,10 @@ private:
     void train_image_step(cudaStream_t s, uint32_t batch_size, bool get_loss);                     // testbed_image.cu:214-285
     void train_sdf_step(cudaStream_t s, uint32_t batch_size, bool get_loss);                       // testbed_sdf.cu:1289-1311
     struct SamplerKey {   // everything generate_training_samples depends on besides the bitfield and the view poses
-        uint32_t step, n_rays, max_inference, target, rank, world, lanes, dataset_version; uint64_t rng_state, rng_inc; float cone; bool snap, max_level_rand; uint32_t cdf_version;
+        uint32_t step, n_rays, max_inference, target, rank, world, lanes, dataset_version; uint64_t rng_state, rng_inc; float cone; bool snap, max_level_rand; uint32_t cdf_version, distortion_version;
         bool operator==(const SamplerKey& o) const {
             return step == o.step && n_rays == o.n_rays && max_inference == o.max_inference && target == o.target && rank == o.rank && world == o.world &&
-                   lanes == o.lanes && dataset_version == o.dataset_version && rng_state == o.rng_state && rng_inc == o.rng_inc && cone == o.cone && snap == o.snap && max_level_rand == o.max_level_rand && cdf_version == o.cdf_version;
+                   lanes == o.lanes && dataset_version == o.dataset_version && rng_state == o.rng_state && rng_inc == o.rng_inc && cone == o.cone && snap == o.snap && max_level_rand == o.max_level_rand && cdf_version == o.cdf_version && distortion_version == o.distortion_version;
         }
     };
     SamplerKey sampler_key(uint32_t n_rays, uint32_t max_inference, uint32_t target) const;
@@ -264,6 +268,11 @@ private:
     // offset, RotationAdamOptimizer for the rotation offset: adam_optimizer.h:143-301), the device gradient accumulators and dL/d(coords)
     std::vector<std::array<float, 24>> m_base_xforms; std::vector<VecAdam> m_cam_pos_offset, m_cam_rot_offset;
     DeviceBuffer m_cam_pos_grad, m_cam_rot_grad, m_coords_gradient;
+    DeviceBuffer m_distortion_map, m_distortion_grad, m_distortion_weight, m_distortion_m1, m_distortion_m2, m_distortion_steps;
+    int m_distortion_res[2] = {32, 32}; std::unique_ptr<Optimizer> m_distortion_opt; bool m_distortion_live = false; uint32_t m_distortion_version = 0;
+    DistortionMap distortion_view() const { DistortionMap d{}; if (m_distortion_live) { d.data = (const float*)m_distortion_map.ptr; d.res[0] = m_distortion_res[0]; d.res[1] = m_distortion_res[1]; } return d; }
+    void ensure_distortion_map(cudaStream_t s);
+    void distortion_step(cudaStream_t s);
     void effective_xform(uint32_t i, float* start12, float* end12);
     void update_transforms(cudaStream_t s, uint32_t first, uint32_t last);   // NerfDataset xforms + offsets -> the poses the kernels see (testbed_nerf.cu:2984-3023)
     void extrinsics_step(cudaStream_t s);

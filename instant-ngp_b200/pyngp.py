@@ -174,7 +174,7 @@ def _stream():
 
 _BOOL_OPTS = {"random_bg_color", "linear_colors", "snap_to_pixel_centers", "train_snap_to_pixel_centers", "shall_train_encoding", "shall_train_network",
               "image_snap_to_pixel_centers", "image_linear_colors", "image_stratified", "prefetch_rays", "dp_sharded_optimizer", "device_control_law",
-              "render_ground_truth", "render_with_lens_distortion", "walk_ahead", "optimize_exposure", "max_level_rand_training", "optimize_extrinsics",
+              "render_ground_truth", "render_with_lens_distortion", "walk_ahead", "optimize_exposure", "max_level_rand_training", "optimize_extrinsics", "optimize_distortion",
               "sample_focal_plane_proportional_to_error", "sample_image_proportional_to_error"}
 _FLOAT_OPTS = {"near_distance", "density_grid_decay", "render_min_transmittance", "cone_angle_constant", "exposure", "zoom", "fov", "ground_truth_alpha",
                "render_near_distance", "exposure_l2_reg", "depth_supervision_lambda", "extrinsic_l2_reg", "extrinsic_learning_rate"}
@@ -351,7 +351,7 @@ class Testbed:
                                      "optimize_exposure": "optimize_exposure", "exposure_l2_reg": "exposure_l2_reg",
                                      "n_steps_between_cam_updates": "n_steps_between_cam_updates",
                                      "depth_supervision_lambda": "depth_supervision_lambda", "depth_loss_type": "depth_loss_type",
-                                     "optimize_extrinsics": "optimize_extrinsics", "extrinsic_l2_reg": "extrinsic_l2_reg",
+                                     "optimize_extrinsics": "optimize_extrinsics", "optimize_distortion": "optimize_distortion", "extrinsic_l2_reg": "extrinsic_l2_reg",
                                      "extrinsic_learning_rate": "extrinsic_learning_rate",
                                      "sample_focal_plane_proportional_to_error": "sample_focal_plane_proportional_to_error",
                                      "sample_image_proportional_to_error": "sample_image_proportional_to_error",

@@ -310,10 +310,27 @@ static inline void opencv_undistort(const float* params, float* u, float* v) {
     }
     *u = x[0]; *v = x[1];
 }
-extern "C" void ref_uv_to_ray(const RefImage* img, const float* uv, float* o, float* d) {
+// The trainable distortion map (Testbed::m_distortion; testbed.cu:4066-4077): process-wide state for the training sampler, the tracer and the camera
+// gradient.  map [h][w][2] fp32 offsets added to a ray direction's image-plane x, y (common_device.cuh:491-493, Buffer2DView::at_lerp common.h:384-400);
+// gradient / gradient_weight (optional) receive deposit_image_gradient's splats (common_device.cuh:124-156; testbed_nerf.cu:2088-2100)
+static const float* g_distortion = nullptr; static int g_distortion_res[2] = {0, 0}; static float* g_distortion_grad = nullptr; static float* g_distortion_weight = nullptr;
+extern "C" void ref_set_distortion(const float* map, int w, int h, float* gradient, float* gradient_weight) {
+    g_distortion = map; g_distortion_res[0] = w; g_distortion_res[1] = h; g_distortion_grad = gradient; g_distortion_weight = gradient_weight;
+}
+static void distortion_at_lerp(float u, float v, float* out) {
+    const int rx = g_distortion_res[0], ry = g_distortion_res[1];
+    float xf = (float)rx * u, yf = (float)ry * v;
+    int x = (int)xf, y = (int)yf; float wx = xf - (float)x, wy = yf - (float)y;
+    auto at = [&](int px, int py, int k) { px = clampi(px, 0, rx - 1); py = clampi(py, 0, ry - 1); return g_distortion[2 * ((size_t)px + (size_t)py * rx) + k]; };
+    for (int k = 0; k < 2; ++k) out[k] = (1 - wx) * (1 - wy) * at(x, y, k) + wx * (1 - wy) * at(x + 1, y, k) + (1 - wx) * wy * at(x, y + 1, k) + wx * wy * at(x + 1, y + 1, k);
+}
+static void uv_to_ray_impl(const RefImage* img, const float* uv, float* o, float* d, bool with_distortion);
+extern "C" void ref_uv_to_ray(const RefImage* img, const float* uv, float* o, float* d) { uv_to_ray_impl(img, uv, o, d, false); }
+static void uv_to_ray_impl(const RefImage* img, const float* uv, float* o, float* d, bool with_distortion) {
     V3 dir = {(uv[0] - img->principal_point[0]) * (float)img->res[0] / img->focal_length[0],
               (uv[1] - img->principal_point[1]) * (float)img->res[1] / img->focal_length[1], 1.0f};
     if (img->lens_mode == REF_LENS_OPENCV) opencv_undistort(img->lens_params, &dir.x, &dir.y);
+    if (with_distortion && g_distortion) { float off[2]; distortion_at_lerp(uv[0], uv[1], off); dir.x += off[0]; dir.y += off[1]; }
     dir = mat3_mul(img->xform, dir);
     o[0] = img->xform[9]; o[1] = img->xform[10]; o[2] = img->xform[11];
     d[0] = dir.x; d[1] = dir.y; d[2] = dir.z;
@@ -564,7 +581,7 @@ extern "C" void ref_generate_training_samples(uint32_t n_rays, const RefAabb* aa
         const float motionblur_time = ref_pcg32_next_float(&rng);   // :1440
         RefImage at_t = *m;                                 // the view with the camera of THIS ray (:1447-1451)
         ref_xform_given_rolling_shutter(m->xform, m->xform_end, m->rolling_shutter, uv[0], uv[1], motionblur_time, at_t.xform);
-        float ro[3], rd[3]; ref_uv_to_ray(&at_t, uv, ro, rd);
+        float ro[3], rd[3]; uv_to_ray_impl(&at_t, uv, ro, rd, true);
         V3 o = ld3(ro), du = ld3(rd);
         if (du.x == 0.f && du.y == 0.f && du.z == 0.f) { o = v3(at_t.xform[9], at_t.xform[10], at_t.xform[11]); du = v3(at_t.xform[6], at_t.xform[7], at_t.xform[8]); }
         V3 d = normalize3(du);
@@ -782,11 +799,11 @@ extern "C" void ref_compute_cam_gradient(uint32_t n_rays, const RefAabb* aabb, u
         const uint32_t n = numsteps[i * 2], base = numsteps[i * 2 + 1];
         if (n == 0) continue;
         const uint32_t img = image_idx(g_ray_offset + ray_indices[i], n_global, n_images);
-        float uv_pdf = 1.0f;
-        if (g_cdf_x_cond_y && g_cam_images) {
+        float uv_pdf = 1.0f; float uv[2] = {0.f, 0.f};
+        if ((g_cdf_x_cond_y || g_distortion_grad) && g_cam_images) {
             RefPcg32 rng; ref_pcg32_seed(&rng, g_cam_seed, 1); ref_pcg32_advance(&rng, (int64_t)g_cam_skip);
             ref_pcg32_advance(&rng, (int64_t)((uint64_t)(g_ray_offset + ray_indices[i]) * REF_N_MAX_RANDOM_SAMPLES_PER_RAY));
-            float uv[2]; random_image_pos_training(&rng, g_cam_images[img].res, g_cam_snap, uv, img, &uv_pdf);
+            random_image_pos_training(&rng, g_cam_images[img].res, g_cam_snap, uv, img, &uv_pdf);
         }
         const V3 ray_o = ld3(rays + (size_t)i * 6), ray_d = normalize3(ld3(rays + (size_t)i * 6 + 3));
         V3 go = v3(0, 0, 0), gd = v3(0, 0, 0);
@@ -799,6 +816,25 @@ extern "C" void ref_compute_cam_gradient(uint32_t n_rays, const RefAabb* aabb, u
             const float t = length3(pos - ray_o);
             const V3 dir_gradient = v3(g[4] * 0.5f, g[5] * 0.5f, g[6] * 0.5f);                                       // warp_direction_derivative
             gd = gd + t * pos_gradient + dir_gradient;
+        }
+        if (g_distortion_grad && g_cam_images) {   // :2088-2100
+            float dp = gd.x * ray_d.x + gd.y * ray_d.y + gd.z * ray_d.z;
+            V3 og = gd - dp * ray_d;
+            const float* m = g_cam_images[img].xform;
+            float a = m[0], b = m[3], c = m[6], d_ = m[1], e = m[4], f = m[7], g = m[2], h = m[5], k = m[8];
+            float id = 1.0f / (a * (e * k - f * h) - b * (d_ * k - f * g) + c * (d_ * h - e * g));
+            float ix = ((e * k - f * h) * og.x + (c * h - b * k) * og.y + (b * f - c * e) * og.z) * id;
+            float iy = ((f * g - d_ * k) * og.x + (a * k - c * g) * og.y + (c * d_ - a * f) * og.z) * id;
+            float val[2] = {ix / uv_pdf, iy / uv_pdf};
+            const int rx = g_distortion_res[0], ry = g_distortion_res[1];
+            float xf = (float)rx * uv[0], yf = (float)ry * uv[1];
+            int tx = (int)xf, ty = (int)yf; float wx = xf - (float)tx, wy = yf - (float)ty;
+            float w4[4] = {(1 - wx) * (1 - wy), wx * (1 - wy), (1 - wx) * wy, wx * wy};
+            for (int q = 0; q < 4; ++q) {
+                int px = clampi(tx + (q & 1), 0, rx - 1), py = clampi(ty + (q >> 1), 0, ry - 1);
+                size_t o = 2 * ((size_t)px + (size_t)py * rx);
+                for (int cc = 0; cc < 2; ++cc) { g_distortion_grad[o + cc] += val[cc] * w4[q]; g_distortion_weight[o + cc] += w4[q]; }
+            }
         }
         if (cam_pos_gradient) { cam_pos_gradient[img * 3] += go.x / uv_pdf; cam_pos_gradient[img * 3 + 1] += go.y / uv_pdf; cam_pos_gradient[img * 3 + 2] += go.z / uv_pdf; }
         if (cam_rot_gradient) {
@@ -889,7 +925,7 @@ extern "C" void ref_render_nerf(const RefRenderCfg* c, const RefNerfNetCfg* net,
         cam.principal_point[0] = c->screen_center[0]; cam.principal_point[1] = c->screen_center[1];
         cam.focal_length[0] = c->focal_length[0]; cam.focal_length[1] = c->focal_length[1];
         memcpy(cam.xform, c->camera, sizeof(cam.xform));
-        float ro[3], rd[3]; ref_uv_to_ray(&cam, uv, ro, rd);
+        float ro[3], rd[3]; uv_to_ray_impl(&cam, uv, ro, rd, true);   // (render_with_lens_distortion: the caller installs the map or not)
         V3 o = ld3(ro), d = normalize3(ld3(rd));
         float oo[3] = {o.x, o.y, o.z}, dd[3] = {d.x, d.y, d.z}, tmm[2];
         ref_aabb_ray_intersect(&c->render_aabb, oo, dd, tmm);

@@ -92,6 +92,9 @@ void ref_generate_training_samples(uint32_t n_rays, const RefAabb* aabb, uint32_
                                    const uint8_t* bitfield, uint32_t max_mip, int snap_to_pixel_centers,
                                    float cone_angle_constant, RefSamplerOut* out);
 
+// The trainable distortion map (Testbed::m_distortion): process-wide state for ref_generate_training_samples / ref_render_nerf (offsets added to the
+// ray directions) and ref_compute_cam_gradient (gradient and weight splats, with ref_set_cam_gradient_rng giving the rays' pixels); NULLs = off
+void ref_set_distortion(const float* map, int w, int h, float* gradient, float* gradient_weight);
 // Error-map importance sampling (testbed.h:733-738): process-wide state for ref_generate_training_samples / ref_compute_loss / ref_compute_cam_gradient.
 // Non-NULL CDFs steer the pixel (cdf_x_cond_y + cdf_y) and / or the view (cdf_img) of every ray; a non-NULL error_map receives the rays' mean losses.
 void ref_set_error_map(const float* cdf_x_cond_y, const float* cdf_y, const float* cdf_img, int cdf_w, int cdf_h, float* error_map, int map_w, int map_h);

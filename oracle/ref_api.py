@@ -341,6 +341,14 @@ def set_error_map(cdf_x_cond_y=None, cdf_y=None, cdf_img=None, cdf_res=(0, 0), e
     fn(q(cdf_x_cond_y), q(cdf_y), q(cdf_img), int(cdf_res[0]), int(cdf_res[1]), q(error_map), int(map_res[0]), int(map_res[1]))
 
 
+def set_distortion(distortion_map=None, gradient=None, gradient_weight=None):
+    """distortion map [h, w, 2] (and optional gradient / weight accumulators of the same shape) for the sampler, the tracer and the camera gradient"""
+    fn = lib().ref_set_distortion; fn.argtypes = [vp, C.c_int, C.c_int, vp, vp]; fn.restype = None
+    q = lambda a: None if a is None else P(a)
+    h, w = (0, 0) if distortion_map is None else distortion_map.shape[:2]
+    fn(q(distortion_map), int(w), int(h), q(gradient), q(gradient_weight))
+
+
 def set_cam_gradient_rng(seed, skip, images, snap):
     fn = lib().ref_set_cam_gradient_rng; fn.argtypes = [u64, u64, vp, C.c_int]; fn.restype = None
     fn(seed, skip, C.cast(images, vp) if images is not None else None, int(snap))

@@ -276,7 +276,8 @@ def test_pyngp_attribute_tree_matches_the_reference_binding(ngp):
         tb.set_camera_to_training_view(0)                  # no data set loaded
     assert tb.nerf.training.dataset.n_images == 0 and tb.nerf.training.n_images_for_training == 0
     assert tb.nerf.training.optimize_extrinsics is False and tb.nerf.training.depth_supervision_lambda == 0.0 and tb.max_level_rand_training is False
-    for name in ("optimize_distortion", "optimize_focal_length", "optimize_extra_dims", "train_envmap"):
+    assert tb.nerf.training.optimize_distortion is False
+    for name in ("optimize_focal_length", "optimize_extra_dims", "train_envmap"):
         with pytest.raises(AttributeError):
             setattr(tb.nerf.training, name, True)           # default-off features outside the path: fail loudly rather than silently
     img = pyngp.Testbed(pyngp.TestbedMode.Image)
