@@ -157,6 +157,8 @@ NerfDataset::NerfDataset(const std::vector<std::string>& json_paths) {
         LensState lens;
         read_lens(json, lens);
         if (json.contains("aabb_scale")) aabb_scale = (int)num(json.at("aabb_scale"));
+        // per-view latent codes (nerf_loader.cu:512-514) widen the network's direction input: not part of this library, refused rather than ignored
+        NGP_CHECK(!json.contains("n_extra_learnable_dims") || num(json.at("n_extra_learnable_dims")) <= 0.f, "n_extra_learnable_dims > 0 (per-view latent codes) is not supported");
         if (json.contains("offset")) {
             const Json& o = json.at("offset");
             for (int k = 0; k < 3; ++k) offset[k] = o.type == Json::Array ? num(o.arr.at(k)) : num(o);

@@ -296,6 +296,7 @@ void Testbed::load_snapshot(cudaStream_t s, const std::string& path) {
             for (size_t i = 0; i < n_img; ++i) { memcpy(m_base_xforms[i].data(), m_host_metas[i].xform, 48); memcpy(m_base_xforms[i].data() + 12, m_host_metas[i].xform_end, 48); }
             m_cam_pos_offset.assign(n_img, VecAdam{}); m_cam_rot_offset.assign(n_img, VecAdam{});
             dataset_from_snapshot = true;
+            NGP_CHECK(d.value("n_extra_learnable_dims", 0.0) <= 0.0, "load_snapshot: a network with per-view latent codes (n_extra_learnable_dims > 0) is not supported");
             aabb_scale = (int)d.value("aabb_scale", (double)aabb_scale);
             m_ds_scale = (float)d.value("scale", (double)m_ds_scale);
             if (d.contains("offset") && d.at("offset").arr.size() == 3) for (int k = 0; k < 3; ++k) m_ds_offset[k] = (float)d.at("offset").arr[k].num;

@@ -134,6 +134,12 @@ def test_aabb_fit_and_errors(L, tmp_path):
     px = np.zeros((6, 8, 4), np.uint8)
     assert lib.ngp_nerf_dataset_set_image(d, 0, px.ctypes.data_as(C.c_void_p), 0, 8, 6) != 0 and b"Couldn't read fov" in lib.ngp_last_error()
     lib.ngp_nerf_dataset_close(d)
+    # per-view latent codes would widen the network input: refused, not ignored
+    (tmp_path / "latents.json").write_text(json.dumps({"x_fov": 40.0, "n_extra_learnable_dims": 4, "frames": [{"file_path": "f0.png", "transform_matrix": _pose(rng)}]}))
+    assert lib.ngp_nerf_dataset_open(str(tmp_path / "latents.json").encode(), C.byref(d)) != 0 and b"n_extra_learnable_dims" in lib.ngp_last_error()
+    (tmp_path / "nolatents.json").write_text(json.dumps({"x_fov": 40.0, "n_extra_learnable_dims": 0, "frames": [{"file_path": "f0.png", "transform_matrix": _pose(rng)}]}))
+    L.check(lib.ngp_nerf_dataset_open(str(tmp_path / "nolatents.json").encode(), C.byref(d)))
+    lib.ngp_nerf_dataset_close(d)
 
 
 @pytest.mark.skipif(not os.path.exists(FOX), reason="reference mount not present (GPU box)")
