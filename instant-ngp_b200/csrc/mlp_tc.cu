@@ -455,7 +455,7 @@ struct BwdParams {
     unsigned long long* probe;   // debug (NGP_MLP_PROBE=1): per CTA [4] = %globaltimer at start / after the prologue / after the tile loop / at exit; null otherwise
 };
 
-template <uint32_t PW, uint32_t DH, uint32_t RH, int MODE>
+template <uint32_t PW, uint32_t DH, uint32_t RH, int MODE, bool TS = false>
 struct BwdCfg {
     static constexpr uint32_t ACC_D0 = 64;                                  // density layer-0 wgrad [64 x PW]
     static constexpr uint32_t ACC_DH = ACC_D0 + PW;                         // density hidden wgrads, 64 cols each
@@ -464,8 +464,10 @@ struct BwdCfg {
     static constexpr uint32_t ACC_RH = ACC_R0 + (MODE == MODE_NERF ? 32 : 0);
     static constexpr uint32_t ACC_RO = ACC_RH + (MODE == MODE_NERF ? 64 * (RH - 1) : 0);
     static constexpr uint32_t ACC_END = ACC_RO + (MODE == MODE_NERF ? 16 : 0);
-    static constexpr uint32_t TMEM_COLS = ACC_END <= 128 ? 128 : (ACC_END <= 256 ? 256 : 512);
-    static_assert(ACC_END <= 512, "network too large for the TMEM-resident wgrad accumulators");
+    static constexpr uint32_t OPA = ACC_END;                                // TS form: 32 columns of packed fp16 pairs, the A operand of the next MMA
+    static constexpr uint32_t COLS_USED = ACC_END + (TS ? 32 : 0);
+    static constexpr uint32_t TMEM_COLS = COLS_USED <= 128 ? 128 : (COLS_USED <= 256 ? 256 : 512);
+    static_assert(COLS_USED <= 512, "network too large for the TMEM-resident wgrad accumulators");
     uint32_t wd[DH + 1], wr[RH + 1], x0, hd[DH], hr[RH], r0, g, go, bars, total;
     __host__ __device__ BwdCfg() {
         SmemCursor c;
@@ -513,27 +515,94 @@ NGP_D void epilogue_masked(uint32_t tmem_row_addr, __half* g, const __half* act,
     }
 }
 
+// ---- "TS" form of the backward kernel (round 2) -------------------------------------------------------------------
+// Every [128 x 64] fp16 tile that is the A operand of the NEXT MMA (forward recompute: the activations; dgrad: the masked
+// gradient G) is written to tensor memory as well as to shared memory, and that MMA reads it from there (tcgen05.mma with
+// A in TMEM): its shared-memory traffic is the B operand alone.  The shared-memory copy stays because the weight-gradient
+// MMAs read both G and the activations MN-major, which only shared memory can serve.  With KEEP the packed activations of
+// the forward recompute also stay in registers until the layer's ReLU' mask has been applied, so the masked epilogue does
+// not read them back from shared memory.  Per 128-sample tile of the NeRF network: 414 -> 286 KB of shared-memory traffic.
+template <bool ST, bool KEEP>
+NGP_D void epilogue_fwd_ts(uint32_t tmem_row_addr, uint32_t opa_row, __half* dst, uint32_t row, uint32_t* keep) {
+    float v[64];
+#pragma unroll
+    for (uint32_t j = 0; j < 64; j += 16) tmem_ld16(tmem_row_addr + j, v + j);
+    tmem_wait_ld();
+    uint32_t pk[32];
+#pragma unroll
+    for (int i = 0; i < 32; ++i) asm("cvt.rn.relu.f16x2.f32 %0, %1, %2;" : "=r"(pk[i]) : "f"(v[2 * i + 1]), "f"(v[2 * i]));
+    if (ST) tmem_st32(opa_row, pk);
+#pragma unroll
+    for (uint32_t c = 0; c < 8; ++c)
+        *reinterpret_cast<uint4*>(dst + blk8_chunk_offset(row, c, MLP_WIDTH)) = make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
+    if (KEEP) {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) keep[i] = pk[i];
+    }
+    if (ST) tmem_wait_st();
+}
+template <bool KEEP>
+NGP_D void epilogue_masked_ts(uint32_t tmem_row_addr, uint32_t opa_row, __half* g, const __half* act, const uint32_t* keep, uint32_t row) {
+    float v[64];
+#pragma unroll
+    for (uint32_t j = 0; j < 64; j += 16) tmem_ld16(tmem_row_addr + j, v + j);
+    uint32_t a[32];
+    if (KEEP) {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) a[i] = keep[i];
+    } else {
+#pragma unroll
+        for (uint32_t c = 0; c < 8; ++c) {
+            const uint4 t = *reinterpret_cast<const uint4*>(act + blk8_chunk_offset(row, c, MLP_WIDTH));
+            a[4 * c] = t.x; a[4 * c + 1] = t.y; a[4 * c + 2] = t.z; a[4 * c + 3] = t.w;
+        }
+    }
+    tmem_wait_ld();
+    uint32_t pk[32];
+    const __half2 zero = __float2half2_rn(0.0f);
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+        asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(pk[i]) : "f"(v[2 * i + 1]), "f"(v[2 * i]));
+        pk[i] &= __hgt2_mask(*reinterpret_cast<const __half2*>(&a[i]), zero);
+    }
+    tmem_st32(opa_row, pk);
+#pragma unroll
+    for (uint32_t c = 0; c < 8; ++c)
+        *reinterpret_cast<uint4*>(g + blk8_chunk_offset(row, c, MLP_WIDTH)) = make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
+    tmem_wait_st();
+}
+
 // Backward through one chain (H hidden layers, input tile IN of CIN columns).  On return, if NEED_DIN, the TMEM work
 // accumulator (cols [0, CIN)) holds dL/dIN for this tile.
-template <uint32_t H, uint32_t CIN, bool NEED_DIN>
+template <uint32_t H, uint32_t CIN, bool NEED_DIN, bool TS = false, bool KEEP = false>
 NGP_D void bwd_chain(StageSync& stage, uint32_t tmem_base, uint32_t tmem_row, uint32_t sbase, uint8_t* smem, uint32_t acc0, uint32_t acch,
                      uint32_t acco, uint32_t in_off, const uint32_t* act_off, uint32_t g_off, uint32_t go_off, const uint32_t* w_off,
-                     uint32_t accumulate, uint32_t tid) {
+                     uint32_t accumulate, uint32_t tid, uint32_t opa_col = 0, const uint32_t* keep = nullptr) {
     const Operand G = {sbase + g_off, MLP_WIDTH}, GO = {sbase + go_off, 16}, IN = {sbase + in_off, CIN};
     __half* g = reinterpret_cast<__half*>(smem + g_off);
+    const uint32_t opa = tmem_base + opa_col, opa_row = tmem_row + opa_col;
     {   // output layer: wgrad^T [64 x 16] += act[H-1]^T * GO ; dgrad [128 x 64] = GO * W_out
         const Operand A = {sbase + act_off[H - 1], MLP_WIDTH}, W = {sbase + w_off[H], MLP_WIDTH};
         stage.run([&] { gemm_pT_q<16>(tmem_base + acco, A, 0, GO, 0, accumulate); gemm_act_w<64>(tmem_base, GO, W, 16); });
-        epilogue_masked(tmem_row, g, reinterpret_cast<const __half*>(smem + act_off[H - 1]), tid);
+        if (TS) epilogue_masked_ts<KEEP>(tmem_row, opa_row, g, reinterpret_cast<const __half*>(smem + act_off[H - 1]), keep + (H - 1) * 32, tid);
+        else epilogue_masked(tmem_row, g, reinterpret_cast<const __half*>(smem + act_off[H - 1]), tid);
     }
+#pragma unroll
     for (uint32_t l = H - 1; l >= 1; --l) {   // hidden layer l: wgrad [64 x 64] += G^T * act[l-1] ; dgrad = G * W_l
         const Operand A = {sbase + act_off[l - 1], MLP_WIDTH}, W = {sbase + w_off[l], MLP_WIDTH};
-        stage.run([&] { gemm_pT_q<64>(tmem_base + acch + 64 * (l - 1), G, 0, A, 0, accumulate); gemm_act_w<64>(tmem_base, G, W, 64); });
-        epilogue_masked(tmem_row, g, reinterpret_cast<const __half*>(smem + act_off[l - 1]), tid);
+        stage.run([&] {
+            gemm_pT_q<64>(tmem_base + acch + 64 * (l - 1), G, 0, A, 0, accumulate);
+            if (TS) gemm_tmem_w<64>(tmem_base, opa, W, 64); else gemm_act_w<64>(tmem_base, G, W, 64);
+        });
+        if (TS) epilogue_masked_ts<KEEP>(tmem_row, opa_row, g, reinterpret_cast<const __half*>(smem + act_off[l - 1]), keep + (l - 1) * 32, tid);
+        else epilogue_masked(tmem_row, g, reinterpret_cast<const __half*>(smem + act_off[l - 1]), tid);
     }
     {   // first layer: wgrad [64 x CIN] += G^T * IN ; dgrad [128 x CIN] = G * W_0
         const Operand W = {sbase + w_off[0], CIN};
-        stage.run([&] { gemm_pT_q<CIN>(tmem_base + acc0, G, 0, IN, 0, accumulate); if (NEED_DIN) gemm_act_w<CIN>(tmem_base, G, W, 64); });
+        stage.run([&] {
+            gemm_pT_q<CIN>(tmem_base + acc0, G, 0, IN, 0, accumulate);
+            if (NEED_DIN) { if (TS) gemm_tmem_w<CIN>(tmem_base, opa, W, 64); else gemm_act_w<CIN>(tmem_base, G, W, 64); }
+        });
     }
 }
 
@@ -559,11 +628,11 @@ NGP_D void flush_wgrad(uint32_t tmem_row, uint32_t col, float* dst, uint32_t ld,
     }
 }
 
-template <uint32_t PW, uint32_t DH, uint32_t RH, int MODE, bool NEED_DENC>
+template <uint32_t PW, uint32_t DH, uint32_t RH, int MODE, bool NEED_DENC, bool TS = false, bool KEEP = false>
 __global__ void __launch_bounds__(128) mlp_backward_kernel(const BwdParams p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);
-    using Cfg = BwdCfg<PW, DH, RH, MODE>;
+    using Cfg = BwdCfg<PW, DH, RH, MODE, TS>;
     const Cfg L;
     const uint32_t tid = threadIdx.x, warp = tid >> 5;
     uint64_t* bar_full = reinterpret_cast<uint64_t*>(smem + L.bars);
@@ -581,10 +650,12 @@ __global__ void __launch_bounds__(128) mlp_backward_kernel(const BwdParams p) {
     fence_after_sync();
     const uint32_t tmem_base = *tmem_slot;
     const uint32_t tmem_row = tmem_base + ((warp * 32u) << 16);
+    const uint32_t opa = tmem_base + Cfg::OPA, opa_row = tmem_row + Cfg::OPA;   // TS form: the A-operand columns
     const uint32_t sbase = smem_u32(smem);
     constexpr uint32_t X_BYTES = TILE_ROWS * PW * 2;
     __half* r0 = reinterpret_cast<__half*>(smem + L.r0);
     __half* go = reinterpret_cast<__half*>(smem + L.go);
+    uint32_t keep_d[KEEP ? DH * 32 : 1], keep_r[KEEP ? RH * 32 : 1];            // KEEP: the packed activations of the forward recompute
 
     stamp(1);
     StageSync stage{bar_mma, 0};
@@ -602,26 +673,55 @@ __global__ void __launch_bounds__(128) mlp_backward_kernel(const BwdParams p) {
 
         // ---- forward recompute: density / plain chain ----
         stage.run([&] { gemm_act_wT<64>(tmem_base, Operand{sbase + L.x0, PW}, 0, Operand{sbase + L.wd[0], PW}, PW); });
-        epilogue_to_smem<64, true>(tmem_row, reinterpret_cast<__half*>(smem + L.hd[0]), MLP_WIDTH, 0, tid);
+        // TS: a layer's activations also go to the TMEM operand columns when a forward layer follows (its A operand)
+        if (TS) { if (DH > 1 || MODE == MODE_NERF) epilogue_fwd_ts<true, KEEP>(tmem_row, opa_row, reinterpret_cast<__half*>(smem + L.hd[0]), tid, keep_d);
+                  else epilogue_fwd_ts<false, KEEP>(tmem_row, opa_row, reinterpret_cast<__half*>(smem + L.hd[0]), tid, keep_d); }
+        else epilogue_to_smem<64, true>(tmem_row, reinterpret_cast<__half*>(smem + L.hd[0]), MLP_WIDTH, 0, tid);
+#pragma unroll
         for (uint32_t l = 1; l < DH; ++l) {
-            stage.run([&] { gemm_act_wT<64>(tmem_base, Operand{sbase + L.hd[l - 1], MLP_WIDTH}, 0, Operand{sbase + L.wd[l], MLP_WIDTH}, MLP_WIDTH); });
-            epilogue_to_smem<64, true>(tmem_row, reinterpret_cast<__half*>(smem + L.hd[l]), MLP_WIDTH, 0, tid);
+            stage.run([&] {
+                if (TS) gemm_tmem_wT<64>(tmem_base, opa, Operand{sbase + L.wd[l], MLP_WIDTH}, MLP_WIDTH);
+                else gemm_act_wT<64>(tmem_base, Operand{sbase + L.hd[l - 1], MLP_WIDTH}, 0, Operand{sbase + L.wd[l], MLP_WIDTH}, MLP_WIDTH);
+            });
+            if (TS) { if (l + 1 < DH || MODE == MODE_NERF) epilogue_fwd_ts<true, KEEP>(tmem_row, opa_row, reinterpret_cast<__half*>(smem + L.hd[l]), tid, keep_d + (KEEP ? l * 32 : 0));
+                      else epilogue_fwd_ts<false, KEEP>(tmem_row, opa_row, reinterpret_cast<__half*>(smem + L.hd[l]), tid, keep_d + (KEEP ? l * 32 : 0)); }
+            else epilogue_to_smem<64, true>(tmem_row, reinterpret_cast<__half*>(smem + L.hd[l]), MLP_WIDTH, 0, tid);
         }
         if (MODE == MODE_NERF) {
-            stage.run([&] { gemm_act_wT<16>(tmem_base, Operand{sbase + L.hd[DH - 1], MLP_WIDTH}, 0, Operand{sbase + L.wd[DH], MLP_WIDTH}, MLP_WIDTH); });
+            stage.run([&] {
+                if (TS) gemm_tmem_wT<16>(tmem_base, opa, Operand{sbase + L.wd[DH], MLP_WIDTH}, MLP_WIDTH);
+                else gemm_act_wT<16>(tmem_base, Operand{sbase + L.hd[DH - 1], MLP_WIDTH}, 0, Operand{sbase + L.wd[DH], MLP_WIDTH}, MLP_WIDTH);
+            });
             float dout[16];
             tmem_ld16(tmem_row, dout); tmem_wait_ld();
-            *reinterpret_cast<uint4*>(r0 + blk8_chunk_offset(tid, 0, 32)) = pack8(dout, false);
-            *reinterpret_cast<uint4*>(r0 + blk8_chunk_offset(tid, 1, 32)) = pack8(dout + 8, false);
             float sh[16]; sh4(dir[0], dir[1], dir[2], sh);
-            *reinterpret_cast<uint4*>(r0 + blk8_chunk_offset(tid, 2, 32)) = pack8(sh, false);
-            *reinterpret_cast<uint4*>(r0 + blk8_chunk_offset(tid, 3, 32)) = pack8(sh + 8, false);
+            const uint4 q0 = pack8(dout, false), q1 = pack8(dout + 8, false), q2 = pack8(sh, false), q3 = pack8(sh + 8, false);
+            if (TS) {
+                const uint32_t pk[16] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, q3.x, q3.y, q3.z, q3.w};
+                tmem_st16(opa_row, pk);
+            }
+            *reinterpret_cast<uint4*>(r0 + blk8_chunk_offset(tid, 0, 32)) = q0;
+            *reinterpret_cast<uint4*>(r0 + blk8_chunk_offset(tid, 1, 32)) = q1;
+            *reinterpret_cast<uint4*>(r0 + blk8_chunk_offset(tid, 2, 32)) = q2;
+            *reinterpret_cast<uint4*>(r0 + blk8_chunk_offset(tid, 3, 32)) = q3;
+            if (TS) tmem_wait_st();
             // ---- forward recompute: rgb hidden layers (the rgb output itself is not needed) ----
-            stage.run([&] { gemm_act_wT<64>(tmem_base, Operand{sbase + L.r0, 32}, 0, Operand{sbase + L.wr[0], 32}, 32); });
-            epilogue_to_smem<64, true>(tmem_row, reinterpret_cast<__half*>(smem + L.hr[0]), MLP_WIDTH, 0, tid);
+            stage.run([&] {
+                if (TS) gemm_tmem_wT<64>(tmem_base, opa, Operand{sbase + L.wr[0], 32}, 32);
+                else gemm_act_wT<64>(tmem_base, Operand{sbase + L.r0, 32}, 0, Operand{sbase + L.wr[0], 32}, 32);
+            });
+            if (TS) { if (RH > 1) epilogue_fwd_ts<true, KEEP>(tmem_row, opa_row, reinterpret_cast<__half*>(smem + L.hr[0]), tid, keep_r);
+                      else epilogue_fwd_ts<false, KEEP>(tmem_row, opa_row, reinterpret_cast<__half*>(smem + L.hr[0]), tid, keep_r); }
+            else epilogue_to_smem<64, true>(tmem_row, reinterpret_cast<__half*>(smem + L.hr[0]), MLP_WIDTH, 0, tid);
+#pragma unroll
             for (uint32_t l = 1; l < RH; ++l) {
-                stage.run([&] { gemm_act_wT<64>(tmem_base, Operand{sbase + L.hr[l - 1], MLP_WIDTH}, 0, Operand{sbase + L.wr[l], MLP_WIDTH}, MLP_WIDTH); });
-                epilogue_to_smem<64, true>(tmem_row, reinterpret_cast<__half*>(smem + L.hr[l]), MLP_WIDTH, 0, tid);
+                stage.run([&] {
+                    if (TS) gemm_tmem_wT<64>(tmem_base, opa, Operand{sbase + L.wr[l], MLP_WIDTH}, MLP_WIDTH);
+                    else gemm_act_wT<64>(tmem_base, Operand{sbase + L.hr[l - 1], MLP_WIDTH}, 0, Operand{sbase + L.wr[l], MLP_WIDTH}, MLP_WIDTH);
+                });
+                if (TS) { if (l + 1 < RH) epilogue_fwd_ts<true, KEEP>(tmem_row, opa_row, reinterpret_cast<__half*>(smem + L.hr[l]), tid, keep_r + (KEEP ? l * 32 : 0));
+                          else epilogue_fwd_ts<false, KEEP>(tmem_row, opa_row, reinterpret_cast<__half*>(smem + L.hr[l]), tid, keep_r + (KEEP ? l * 32 : 0)); }
+                else epilogue_to_smem<64, true>(tmem_row, reinterpret_cast<__half*>(smem + L.hr[l]), MLP_WIDTH, 0, tid);
             }
             // ---- dL/d(rgb out): extract_rgb (nerf_network.h:45-60) — only channels 0..2 feed the rgb net ----
             const uint2 graw = __ldg(reinterpret_cast<const uint2*>(p.dL_dout + (size_t)row_g * 4));
@@ -632,7 +732,7 @@ __global__ void __launch_bounds__(128) mlp_backward_kernel(const BwdParams p) {
                 *reinterpret_cast<uint4*>(go + blk8_chunk_offset(tid, 0, 16)) = *reinterpret_cast<uint4*>(c0);
                 *reinterpret_cast<uint4*>(go + blk8_chunk_offset(tid, 1, 16)) = make_uint4(0, 0, 0, 0);
             }
-            bwd_chain<RH, 32, true>(stage, tmem_base, tmem_row, sbase, smem, Cfg::ACC_R0, Cfg::ACC_RH, Cfg::ACC_RO, L.r0, L.hr, L.g, L.go, L.wr, accumulate, tid);
+            bwd_chain<RH, 32, true, TS, KEEP>(stage, tmem_base, tmem_row, sbase, smem, Cfg::ACC_R0, Cfg::ACC_RH, Cfg::ACC_RO, L.r0, L.hr, L.g, L.go, L.wr, accumulate, tid, Cfg::OPA, keep_r);
             if (p.dL_dcoords) {   // d(rgb input)[16:32] = dL/d(SH4(dir)), stored in network precision by the reference, -> dL/d(dir)
                 float gsh[16];
                 tmem_ld16(tmem_row + 16, gsh); tmem_wait_ld();
@@ -653,7 +753,7 @@ __global__ void __launch_bounds__(128) mlp_backward_kernel(const BwdParams p) {
             *reinterpret_cast<uint4*>(go + blk8_chunk_offset(tid, 0, 16)) = __ldg(gsrc);
             *reinterpret_cast<uint4*>(go + blk8_chunk_offset(tid, 1, 16)) = __ldg(gsrc + 1);
         }
-        bwd_chain<DH, PW, NEED_DENC>(stage, tmem_base, tmem_row, sbase, smem, Cfg::ACC_D0, Cfg::ACC_DH, Cfg::ACC_DO, L.x0, L.hd, L.g, L.go, L.wd, accumulate, tid);
+        bwd_chain<DH, PW, NEED_DENC, TS, KEEP>(stage, tmem_base, tmem_row, sbase, smem, Cfg::ACC_D0, Cfg::ACC_DH, Cfg::ACC_DO, L.x0, L.hd, L.g, L.go, L.wd, accumulate, tid, Cfg::OPA, keep_d);
         // X0 is free now: prefetch the next tile's input while the last epilogue runs
         const uint32_t next = tile + gridDim.x;
         if (tid == 0 && next < p.n_tiles) {
@@ -752,13 +852,22 @@ static void launch_fwd(cudaStream_t s, const FwdParams& p) {
     NGP_POST_LAUNCH();
 }
 
-template <uint32_t PW, uint32_t DH, uint32_t RH, int MODE>
-static void launch_bwd(cudaStream_t s, const BwdParams& p) {
-    const BwdCfg<PW, DH, RH, MODE> L;
+// NGP_MLP_BWD = 0 (default): every operand in shared memory; 1: TS form; 2 (builds with -DNGP_MLP_BWD_KEEP only): TS form + activations kept in
+// registers.  Measured on B200 (profiles/r02_mlp_bwd_forms.txt): 0.0605 / 0.0598 / 0.0618 ms per 2^18 samples — the kernel is bound by the
+// length of its per-tile dependency chain (9 MMA stages x ~1.3 k cycles at 2 CTAs per SM), not by shared-memory traffic, so form 0 stays.
+static int mlp_bwd_form() {
+    static const int v = [] { const char* e = getenv("NGP_MLP_BWD"); return e ? atoi(e) : 0; }();
+    return v;
+}
+
+template <uint32_t PW, uint32_t DH, uint32_t RH, int MODE, bool TS, bool KEEP>
+static void launch_bwd_form(cudaStream_t s, const BwdParams& p) {
+    using Cfg = BwdCfg<PW, DH, RH, MODE, TS>;
+    const Cfg L;
     static const bool probe = getenv("NGP_MLP_PROBE") != nullptr;
     if (probe && p.dL_denc && p.n_tiles >= 1024) {   // debug: where the kernel's wall time goes, from per-CTA %globaltimer stamps (ns), to stderr
-        auto k = mlp_backward_kernel<PW, DH, RH, MODE, true>;
-        const uint32_t grid = persistent_grid(k, L.total, BwdCfg<PW, DH, RH, MODE>::TMEM_COLS, p.n_tiles);
+        auto k = mlp_backward_kernel<PW, DH, RH, MODE, true, TS, KEEP>;
+        const uint32_t grid = persistent_grid(k, L.total, Cfg::TMEM_COLS, p.n_tiles);
         BwdParams q = p; unsigned long long* d = nullptr; std::vector<unsigned long long> h((size_t)grid * 4);
         NGP_CUDA_CHECK(cudaMalloc(&d, h.size() * 8)); q.probe = d;
         k<<<grid, 128, L.total, s>>>(q);
@@ -772,15 +881,26 @@ static void launch_bwd(cudaStream_t s, const BwdParams& p) {
         return;
     }
     if (p.dL_denc) {
-        auto k = mlp_backward_kernel<PW, DH, RH, MODE, true>;
-        const uint32_t grid = persistent_grid(k, L.total, BwdCfg<PW, DH, RH, MODE>::TMEM_COLS, p.n_tiles);
+        auto k = mlp_backward_kernel<PW, DH, RH, MODE, true, TS, KEEP>;
+        const uint32_t grid = persistent_grid(k, L.total, Cfg::TMEM_COLS, p.n_tiles);
         k<<<grid, 128, L.total, s>>>(p);
     } else {
-        auto k = mlp_backward_kernel<PW, DH, RH, MODE, false>;
-        const uint32_t grid = persistent_grid(k, L.total, BwdCfg<PW, DH, RH, MODE>::TMEM_COLS, p.n_tiles);
+        auto k = mlp_backward_kernel<PW, DH, RH, MODE, false, TS, KEEP>;
+        const uint32_t grid = persistent_grid(k, L.total, Cfg::TMEM_COLS, p.n_tiles);
         k<<<grid, 128, L.total, s>>>(p);
     }
     NGP_POST_LAUNCH();
+}
+
+template <uint32_t PW, uint32_t DH, uint32_t RH, int MODE>
+static void launch_bwd(cudaStream_t s, const BwdParams& p) {
+    switch (mlp_bwd_form()) {
+        case 1: launch_bwd_form<PW, DH, RH, MODE, true, false>(s, p); break;
+#ifdef NGP_MLP_BWD_KEEP   // not built by default: 224 registers per thread and measured slower (profiles/r02_mlp_bwd_forms.txt)
+        case 2: launch_bwd_form<PW, DH, RH, MODE, true, true>(s, p); break;
+#endif
+        default: launch_bwd_form<PW, DH, RH, MODE, false, false>(s, p); break;
+    }
 }
 
 #define NERF_DISPATCH(FN, MODE, d, ...)                                                                          \

@@ -17,10 +17,6 @@ __device__ __forceinline__ bool elect_one() {
     asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
     return pred != 0;
 }
-__device__ __forceinline__ void umma_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
-    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
-                 ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
-}
 
 constexpr int NRES = 32;
 struct Result { long long cyc[NRES]; };
@@ -181,6 +177,52 @@ __global__ void __launch_bounds__(128) ubench2_kernel(Result* out) {
     }
     ++slot;   // 10
 
+    // ---- V8: weight-gradient form (gemm_pT_q): M = 64, A and B both MN-major over a [128 x 64] tile, K = 128 in 8 steps, dependent ----
+    // ---- V9: dgrad form (gemm_act_w): M = 128, A K-major, B MN-major, 4 steps ----
+    {
+        constexpr uint32_t NW = N > 64 ? 64 : N;
+        constexpr uint32_t idesc_w = make_idesc(64, NW, 1, 1), idesc_g = make_idesc(128, NW, 0, 1);
+        uint64_t pa[8], qb[8], gb[4];
+#pragma unroll
+        for (int r = 0; r < 8; ++r) { pa[r] = desc_mnmajor(A, 0, r * 16); qb[r] = desc_mnmajor(B, 0, r * 16); }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) gb[k] = desc_mnmajor(B, 0, k * 16);
+        for (int rep = 0; rep < 2; ++rep) {
+            SYNC_ALL(); t0 = clock64();
+            if (warp == 0) {
+                if (elect_one()) {
+#pragma unroll
+                    for (int r = 0; r < REP; ++r) {
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) umma(tbase + 64, pa[k], qb[k], idesc_w, (k | r) > 0);
+                    }
+                    umma_commit(&bar);
+                }
+                __syncwarp();
+            }
+            mbar_wait(&bar, parity); parity ^= 1u; fence_after_sync(); t1 = clock64();
+            if (tid == 0 && rep == 1) res->cyc[slot] = t1 - t0;
+        }
+        ++slot;   // 11
+        for (int rep = 0; rep < 2; ++rep) {
+            SYNC_ALL(); t0 = clock64();
+            if (warp == 0) {
+                if (elect_one()) {
+#pragma unroll
+                    for (int r = 0; r < REP; ++r) {
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) umma(tbase, ad[k], gb[k], idesc_g, (k | r) > 0);
+                    }
+                    umma_commit(&bar);
+                }
+                __syncwarp();
+            }
+            mbar_wait(&bar, parity); parity ^= 1u; fence_after_sync(); t1 = clock64();
+            if (tid == 0 && rep == 1) res->cyc[slot] = t1 - t0;
+        }
+        ++slot;   // 12
+    }
+
     if (keep == 123.456f) res->cyc[NRES - 1] = 1;
     fence_before_sync(); __syncthreads();
     if (warp == 0) tmem_dealloc<512>(tbase);
@@ -203,11 +245,13 @@ static void run(int grid) {
     printf("  V5 round-1 StageSync round trip (fence, __syncthreads, tid==0 issues 4 MMAs, commit, all wait): %.0f cycles\n", c[6] / (double)REP);
     printf("  V6 epilogue per 128x64 tile (4 warps): ld+wait %.0f, +relu/pack+st.shared %.0f, +relu/pack+tcgen05.st %.0f cycles\n", c[7] / (double)REP, c[8] / (double)REP, c[9] / (double)REP);
     printf("  V7 TS mode (A in TMEM) uniform issue dependent chain                        : %lld  (%.1f / MMA)\n", c[10], c[10] / n);
+    printf("  V8 wgrad form M64 N%u, A and B MN-major, 8 K-steps, dependent chain             : %lld  (%.1f / MMA)\n", N > 64 ? 64 : N, c[11], c[11] / (REP * 8.0));
+    printf("  V9 dgrad form M128 N%u, A K-major, B MN-major, dependent chain                   : %lld  (%.1f / MMA)\n", N > 64 ? 64 : N, c[12], c[12] / n);
     cudaFree(d);
 }
 
 int main(int argc, char** argv) {
     const int grid = argc > 1 ? atoi(argv[1]) : 148;
-    run<64>(grid); run<16>(grid); run<256>(grid);
+    run<64>(grid); run<16>(grid); run<32>(grid); run<256>(grid);
     return 0;
 }
