@@ -303,18 +303,19 @@ def run_own(args):
     def timed(steps, upload):
         """EXACTLY `steps` steps between two CUDA events, barrier + synchronize on both sides; returns (ms max over ranks, samples
         summed over ranks, samples before compaction, launches)"""
-        n = 0; nb = 0
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         barrier()
+        # the library reads each step's two sample counters back to pinned host memory (and the loss every 16th step, testbed.cu:4349) and
+        # consumes them on the host before the next step starts; their running sums are read once per window instead of once per step
+        n0, nb0 = tb.get_option("measured_batch_size_total"), tb.get_option("measured_batch_size_before_compaction_total")
         l0 = lib.ngp_kernel_launch_count()
         e0.record()
         for i in range(steps):
             if upload:
                 tb.set_training_image(i % len(views), views[i % len(views)]["pixels"])    # H2D from pinned host memory
             tb.train(batch)
-            st = tb.stats                                                                  # host copy of the counters read back by train()
-            n += st.measured_batch_size; nb += st.measured_batch_size_before_compaction
-            _ = st.loss
+        n = int(tb.get_option("measured_batch_size_total") - n0)                           # (waits for the last step's counters)
+        nb = int(tb.get_option("measured_batch_size_before_compaction_total") - nb0)
         e1.record()
         barrier()
         ms = e0.elapsed_time(e1)
@@ -438,7 +439,7 @@ def run_own(args):
             "windows": {"repeats": len(rows), "steps_each": args.steps, "value_median": rate(rows[len(rows) // 2]), "value_min": rate(rows[0]), "value_max": rate(rows[-1]),
                         "ms_per_step_min": min(r[0] for r in rows) / args.steps, "ms_per_step_max": max(r[0] for r in rows) / args.steps},
             "e2e": {"value": n_e2e / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": view_bytes, "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / args.steps,
-                    "api": "pyngp.Testbed.set_training_image + train + loss", "repeats": len(rows_e2e), "value_min": rate(rows_e2e[0]), "value_max": rate(rows_e2e[-1])},
+                    "api": "pyngp.Testbed.set_training_image + train (the library reads the counters back every step, the loss every 16th)", "repeats": len(rows_e2e), "value_min": rate(rows_e2e[0]), "value_max": rate(rows_e2e[-1])},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "kernels": kernels}
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         state = trained_state(tb)

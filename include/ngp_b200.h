@@ -40,6 +40,10 @@ int ngp_profile_timeline(char* buf, uint64_t buf_size);
  * red.global.add.f16x2 lanes per second (`vec` = 4-byte entries per lane: 1, 2 or 4).  Median of `reps` launches. */
 int ngp_microbench_l2_gather(void* stream, uint64_t buffer_bytes, uint32_t reps, double* gathers_per_s);
 int ngp_microbench_l2_red(void* stream, uint64_t buffer_bytes, int32_t vec, uint32_t reps, double* lanes_per_s);
+/* Host-side test ngp_testbed_set_training_image applies to an RGBA8 view before it keeps a prefetched walk: does the view contain the
+ * mask colour 0x00FF00FF of read_rgba (common_device.cuh:885-913)?  Exposed for tests (the scan reads eight interleaved streams: as one
+ * linear stream it made the upload path host-bound).  No device needed. */
+int ngp_host_has_mask_pixels(const void* rgba8_pixels, uint64_t n_pixels, int32_t* has_mask);
 
 /* activation layouts for encoder outputs / MLP inputs */
 enum { NGP_LAYOUT_ROWMAJOR = 0, /* [n][C] fp16 ("AoS", tcnn::RM with one sample per row) */

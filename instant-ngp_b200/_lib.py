@@ -61,6 +61,7 @@ SYMBOLS = {
     "ngp_profile_timeline": (i32, [cp, u64]),
     "ngp_microbench_l2_gather": (i32, [vp, u64, u32, C.POINTER(C.c_double)]),
     "ngp_microbench_l2_red": (i32, [vp, u64, i32, u32, C.POINTER(C.c_double)]),
+    "ngp_host_has_mask_pixels": (i32, [vp, u64, C.POINTER(i32)]),
     "ngp_encoding_create": (i32, [cp, u32, C.POINTER(vp)]),
     "ngp_encoding_destroy": (None, [vp]),
     "ngp_encoding_n_params": (u64, [vp]),

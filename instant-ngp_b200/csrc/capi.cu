@@ -47,6 +47,11 @@ extern "C" {
 const char* ngp_last_error(void) { return g_last_error.c_str(); }
 int ngp_abi_version(void) { return NGP_B200_ABI_VERSION; }
 uint64_t ngp_kernel_launch_count(void) { return g_launch_count.load(); }
+int ngp_host_has_mask_pixels(const void* rgba8_pixels, uint64_t n_pixels, int32_t* has_mask) {
+    NGP_API_BEGIN NGP_CHECK(has_mask && (rgba8_pixels || n_pixels == 0), "null argument");
+    *has_mask = host_has_mask_pixels(rgba8_pixels, (size_t)n_pixels) ? 1 : 0;
+    NGP_API_END
+}
 void ngp_profile_enable(int on) { profile_enable(on != 0); }
 int ngp_profile_report(char* buf, uint64_t buf_size, int reset) {
     NGP_API_BEGIN NGP_CHECK(buf && buf_size > 2, "null argument");
@@ -213,6 +218,9 @@ int ngp_adam_step(void* stream, const ngp_adam_hyper* h, uint64_t n, void* maste
 
 // ---- Testbed ----
 struct ngp_testbed { Testbed tb; explicit ngp_testbed(int mode) : tb(mode) {} };
+// every entry point sees the testbed with its last step finished on the host side (Testbed::finish_pending_step), except
+// ngp_testbed_set_training_image: the upload between two steps must not make the host wait for the device
+static inline Testbed& TB(ngp_testbed_t t) { t->tb.finish_pending_step(); return t->tb; }
 
 extern "C" {
 
@@ -224,22 +232,22 @@ int ngp_testbed_create(int mode, ngp_testbed_t* out) {
 void ngp_testbed_destroy(ngp_testbed_t t) { delete t; }
 int ngp_testbed_reload_network_from_json(ngp_testbed_t t, const char* json) {
     NGP_API_BEGIN require_device(); NGP_CHECK(t && json, "null argument");
-    t->tb.reload_network_from_json(json);
+    TB(t).reload_network_from_json(json);
     NGP_API_END
 }
 int ngp_testbed_reload_network_from_json_base(ngp_testbed_t t, const char* json, const char* config_base_path) {
     NGP_API_BEGIN require_device(); NGP_CHECK(t && json, "null argument");
-    t->tb.reload_network_from_json(json, config_base_path ? config_base_path : "");
+    TB(t).reload_network_from_json(json, config_base_path ? config_base_path : "");
     NGP_API_END
 }
 int ngp_testbed_reload_network_from_file(ngp_testbed_t t, const char* path) {
     NGP_API_BEGIN require_device(); NGP_CHECK(t, "null argument");
-    t->tb.reload_network_from_file(path ? path : "");
+    TB(t).reload_network_from_file(path ? path : "");
     NGP_API_END
 }
 int ngp_testbed_set_root_dir(ngp_testbed_t t, const char* root_dir) {
     NGP_API_BEGIN NGP_CHECK(t && root_dir, "null argument");
-    t->tb.root_dir = root_dir;
+    TB(t).root_dir = root_dir;
     NGP_API_END
 }
 int ngp_builtin_base_config(int32_t mode, const char** json) {
@@ -250,7 +258,7 @@ int ngp_builtin_base_config(int32_t mode, const char** json) {
 int ngp_testbed_set_nerf_dataset(ngp_testbed_t t, void* stream, uint32_t n_images, const ngp_training_image* images, int32_t aabb_scale) {
     NGP_API_BEGIN require_device(); NGP_CHECK(t && images, "null argument");
     static_assert(sizeof(ngp_training_image) == sizeof(HostImage), "ABI struct mismatch");
-    t->tb.set_nerf_dataset(S(stream), n_images, reinterpret_cast<const HostImage*>(images), aabb_scale);
+    TB(t).set_nerf_dataset(S(stream), n_images, reinterpret_cast<const HostImage*>(images), aabb_scale);
     NGP_API_END
 }
 int ngp_nerf_dataset_open(const char* json_paths, ngp_nerf_dataset_t* out) {
@@ -313,18 +321,18 @@ int ngp_testbed_load_nerf_dataset(ngp_testbed_t t, void* stream, ngp_nerf_datase
     std::vector<ngp_training_image> views(d->ds.n_images());
     for (size_t i = 0; i < views.size(); ++i) fill_view(d->ds.frames[i], &views[i]);
     static_assert(sizeof(ngp_training_image) == sizeof(HostImage), "ABI struct drift");
-    t->tb.set_nerf_dataset(S(stream), (uint32_t)views.size(), reinterpret_cast<const HostImage*>(views.data()), d->ds.aabb_scale);
-    t->tb.set_dataset_scale_offset(d->ds.scale, d->ds.offset);
-    t->tb.apply_dataset_view_hints(d->ds.has_render_aabb, d->ds.render_aabb, d->ds.up);
+    TB(t).set_nerf_dataset(S(stream), (uint32_t)views.size(), reinterpret_cast<const HostImage*>(views.data()), d->ds.aabb_scale);
+    TB(t).set_dataset_scale_offset(d->ds.scale, d->ds.offset);
+    TB(t).apply_dataset_view_hints(d->ds.has_render_aabb, d->ds.render_aabb, d->ds.up);
     for (size_t i = 0; i < d->ds.frames.size(); ++i) {   // end poses and rolling shutter (already in the NGP convention)
         const ngp::DatasetFrame& f = d->ds.frames[i];
         const bool moving = memcmp(f.xform, f.xform_end, sizeof(f.xform)) != 0;
         const bool shutter = f.rolling_shutter[0] != 0.f || f.rolling_shutter[1] != 0.f || f.rolling_shutter[2] != 0.f || f.rolling_shutter[3] != 0.f;
-        if (moving || shutter) t->tb.set_camera_extrinsics_rolling_shutter(S(stream), (int)i, f.xform, f.xform_end, f.rolling_shutter, false);
+        if (moving || shutter) TB(t).set_camera_extrinsics_rolling_shutter(S(stream), (int)i, f.xform, f.xform_end, f.rolling_shutter, false);
         // depth maps in scene units: integer_depth_scale * scene scale (nerf_loader.cu:711); a data set with a depth scale gives EVERY view a map
         // (zeros where a frame names no depth file)
         const float depth_scale = f.depth_scale * d->ds.scale;
-        if (depth_scale >= 0.f) t->tb.set_training_depth(S(stream), (int)i, f.depth_pixels.empty() ? nullptr : f.depth_pixels.data(), 0, depth_scale);
+        if (depth_scale >= 0.f) TB(t).set_training_depth(S(stream), (int)i, f.depth_pixels.empty() ? nullptr : f.depth_pixels.data(), 0, depth_scale);
     }
     NGP_API_END
 }
@@ -336,43 +344,43 @@ int ngp_testbed_set_training_image(ngp_testbed_t t, void* stream, uint32_t frame
 int ngp_testbed_set_camera_intrinsics(ngp_testbed_t t, void* stream, int32_t frame_idx, float fx, float fy, float cx, float cy,
                                       float k1, float k2, float p1, float p2) {
     NGP_API_BEGIN require_device(); NGP_CHECK(t, "null argument");
-    t->tb.set_camera_intrinsics(S(stream), frame_idx, fx, fy, cx, cy, k1, k2, p1, p2);
+    TB(t).set_camera_intrinsics(S(stream), frame_idx, fx, fy, cx, cy, k1, k2, p1, p2);
     NGP_API_END
 }
 int ngp_testbed_set_camera_extrinsics_rolling_shutter(ngp_testbed_t t, void* stream, int32_t frame_idx, const float* c2w_start, const float* c2w_end,
                                                       const float* rolling_shutter4, int32_t convert_to_ngp) {
     NGP_API_BEGIN require_device(); NGP_CHECK(t && c2w_start && c2w_end && rolling_shutter4, "null argument");
-    t->tb.set_camera_extrinsics_rolling_shutter(S(stream), frame_idx, c2w_start, c2w_end, rolling_shutter4, convert_to_ngp != 0);
+    TB(t).set_camera_extrinsics_rolling_shutter(S(stream), frame_idx, c2w_start, c2w_end, rolling_shutter4, convert_to_ngp != 0);
     NGP_API_END
 }
 int ngp_testbed_set_camera_extrinsics(ngp_testbed_t t, void* stream, int32_t frame_idx, const float* c2w, int32_t convert_to_ngp) {
     NGP_API_BEGIN require_device(); NGP_CHECK(t && c2w, "null argument");
-    t->tb.set_camera_extrinsics(S(stream), frame_idx, c2w, convert_to_ngp != 0);
+    TB(t).set_camera_extrinsics(S(stream), frame_idx, c2w, convert_to_ngp != 0);
     NGP_API_END
 }
 int ngp_testbed_get_camera_extrinsics(ngp_testbed_t t, int32_t frame_idx, int32_t convert_to_ngp, float* out12) {
     NGP_API_BEGIN NGP_CHECK(t && out12, "null argument");
-    t->tb.get_camera_extrinsics(frame_idx, convert_to_ngp != 0, out12);
+    TB(t).get_camera_extrinsics(frame_idx, convert_to_ngp != 0, out12);
     NGP_API_END
 }
 int ngp_testbed_set_training_depth(ngp_testbed_t t, void* stream, int32_t frame_idx, const void* host_depth, int32_t depth_type, float depth_scale) {
     NGP_API_BEGIN require_device(); NGP_CHECK(t, "null argument");
-    t->tb.set_training_depth(S(stream), frame_idx, host_depth, depth_type, depth_scale);
+    TB(t).set_training_depth(S(stream), frame_idx, host_depth, depth_type, depth_scale);
     NGP_API_END
 }
 int ngp_testbed_reset(ngp_testbed_t t, int32_t reset_density_grid) {
     NGP_API_BEGIN require_device(); NGP_CHECK(t, "null argument");
-    t->tb.reset(reset_density_grid != 0);
+    TB(t).reset(reset_density_grid != 0);
     NGP_API_END
 }
 int ngp_testbed_set_image(ngp_testbed_t t, void* stream, const float* rgba, int32_t w, int32_t h) {
     NGP_API_BEGIN require_device(); NGP_CHECK(t && rgba, "null argument");
-    t->tb.set_image(S(stream), rgba, w, h);
+    TB(t).set_image(S(stream), rgba, w, h);
     NGP_API_END
 }
 int ngp_testbed_set_image_rgba8(ngp_testbed_t t, void* stream, const uint8_t* rgba8, int32_t w, int32_t h) {
     NGP_API_BEGIN require_device(); NGP_CHECK(t && rgba8, "null argument");
-    t->tb.set_image_rgba8(S(stream), rgba8, w, h);
+    TB(t).set_image_rgba8(S(stream), rgba8, w, h);
     NGP_API_END
 }
 int ngp_mode_from_scene(const char* path, int32_t* mode) {
@@ -400,27 +408,27 @@ int ngp_snapshot_mode(const char* path, int32_t* mode) {
 int ngp_testbed_override_sdf_training_data(ngp_testbed_t t, void* stream, const float* points, const float* distances, uint32_t n,
                                            const float* raw_aabb_min, const float* raw_aabb_max, float mesh_scale) {
     NGP_API_BEGIN require_device(); NGP_CHECK(t && raw_aabb_min && raw_aabb_max, "null argument");
-    t->tb.override_sdf_training_data(S(stream), points, distances, n, raw_aabb_min, raw_aabb_max, mesh_scale);
+    TB(t).override_sdf_training_data(S(stream), points, distances, n, raw_aabb_min, raw_aabb_max, mesh_scale);
     NGP_API_END
 }
 int ngp_testbed_train(ngp_testbed_t t, void* stream, uint32_t batch) {
     NGP_API_BEGIN require_device(); NGP_CHECK(t, "null argument");
-    t->tb.train(S(stream), batch);
+    TB(t).train(S(stream), batch);
     NGP_API_END
 }
 int ngp_testbed_train_begin(ngp_testbed_t t, void* stream, uint32_t batch) {
     NGP_API_BEGIN require_device(); NGP_CHECK(t, "null argument");
-    t->tb.train_begin(S(stream), batch);
+    TB(t).train_begin(S(stream), batch);
     NGP_API_END
 }
 int ngp_testbed_train_end(ngp_testbed_t t, void* stream, uint32_t measured, uint32_t measured_before) {
     NGP_API_BEGIN require_device(); NGP_CHECK(t, "null argument");
-    t->tb.train_end(S(stream), measured, measured_before);
+    TB(t).train_end(S(stream), measured, measured_before);
     NGP_API_END
 }
 int ngp_testbed_pending_counters(ngp_testbed_t t, uint32_t* measured, uint32_t* measured_before) {
     NGP_API_BEGIN require_device(); NGP_CHECK(t && measured && measured_before, "null argument");
-    t->tb.pending_counters(measured, measured_before);
+    TB(t).pending_counters(measured, measured_before);
     NGP_API_END
 }
 int ngp_comm_unique_id(void* out128, const char* nccl_lib_path) {
@@ -430,22 +438,22 @@ int ngp_comm_unique_id(void* out128, const char* nccl_lib_path) {
 }
 int ngp_testbed_comm_init(ngp_testbed_t t, const void* id128, uint32_t rank, uint32_t world, const char* nccl_lib_path) {
     NGP_API_BEGIN require_device(); NGP_CHECK(t && id128, "null argument");
-    t->tb.comm_init(id128, rank, world, nccl_lib_path);
+    TB(t).comm_init(id128, rank, world, nccl_lib_path);
     NGP_API_END
 }
 int ngp_testbed_set_shard(ngp_testbed_t t, uint32_t rank, uint32_t world) {
     NGP_API_BEGIN NGP_CHECK(t && world >= 1 && rank < world, "bad shard");
-    t->tb.set_shard(rank, world);
+    TB(t).set_shard(rank, world);
     NGP_API_END
 }
 int ngp_testbed_stats(ngp_testbed_t t, ngp_train_stats* out) {
     NGP_API_BEGIN NGP_CHECK(t && out, "null argument");
     static_assert(sizeof(ngp_train_stats) == sizeof(TrainStats), "ABI struct mismatch");
-    TrainStats st = t->tb.stats(); memcpy(out, &st, sizeof(st));
+    TrainStats st = TB(t).stats(); memcpy(out, &st, sizeof(st));
     NGP_API_END
 }
-uint64_t ngp_testbed_n_params(ngp_testbed_t t) { return t ? t->tb.n_params() : 0; }
-uint64_t ngp_testbed_n_encoding_params(ngp_testbed_t t) { Trainer* tr = t ? t->tb.trainer() : nullptr; return tr ? tr->n_params - tr->n_matrix_params : 0; }
+uint64_t ngp_testbed_n_params(ngp_testbed_t t) { return t ? TB(t).n_params() : 0; }
+uint64_t ngp_testbed_n_encoding_params(ngp_testbed_t t) { Trainer* tr = t ? TB(t).trainer() : nullptr; return tr ? tr->n_params - tr->n_matrix_params : 0; }
 int ngp_json_to_msgpack(const char* json, void* out, uint64_t capacity, uint64_t* out_size) {
     NGP_API_BEGIN NGP_CHECK(json && out_size, "null argument");
     std::string bytes; msgpack_encode(Json::parse(json), bytes);
@@ -464,22 +472,22 @@ int ngp_msgpack_roundtrip(const void* in, uint64_t in_size, void* out, uint64_t 
 }
 int ngp_testbed_save_snapshot(ngp_testbed_t t, void* stream, const char* path, int32_t include_optimizer_state, int32_t compress) {
     NGP_API_BEGIN require_device(); NGP_CHECK(t && path, "null argument");
-    t->tb.save_snapshot(S(stream), path, include_optimizer_state != 0, compress != 0);
+    TB(t).save_snapshot(S(stream), path, include_optimizer_state != 0, compress != 0);
     NGP_API_END
 }
 int ngp_testbed_load_snapshot(ngp_testbed_t t, void* stream, const char* path) {
     NGP_API_BEGIN require_device(); NGP_CHECK(t && path, "null argument");
-    t->tb.load_snapshot(S(stream), path);
+    TB(t).load_snapshot(S(stream), path);
     NGP_API_END
 }
 int ngp_testbed_sync_inference_params(ngp_testbed_t t, void* stream) {
     NGP_API_BEGIN NGP_CHECK(t, "null argument"); require_device();
-    t->tb.sync_inference_params(S(stream));
+    TB(t).sync_inference_params(S(stream));
     NGP_API_END
 }
 int ngp_testbed_param_buffer(ngp_testbed_t t, int which, void** ptr, uint64_t* n) {
     NGP_API_BEGIN NGP_CHECK(t && ptr && n, "null argument");
-    Trainer* tr = t->tb.trainer(); NGP_CHECK(tr, "no network loaded");
+    Trainer* tr = TB(t).trainer(); NGP_CHECK(tr, "no network loaded");
     switch (which) { case 0: *ptr = tr->master; break; case 1: *ptr = tr->params; break; case 2: *ptr = tr->inference_params; break;
         case 3: *ptr = tr->grads; break; case 4: *ptr = tr->m; break; case 5: *ptr = tr->v; break; case 6: *ptr = tr->steps; break;
         case 7: *ptr = tr->ema; break; default: throw Error("param_buffer: which must be 0..7"); }
@@ -488,25 +496,25 @@ int ngp_testbed_param_buffer(ngp_testbed_t t, int which, void** ptr, uint64_t* n
 }
 int ngp_testbed_density_grid(ngp_testbed_t t, int which, void** ptr, uint64_t* n_bytes) {
     NGP_API_BEGIN NGP_CHECK(t && ptr && n_bytes, "null argument");
-    if (which == 0) { *ptr = (void*)t->tb.density_grid(); *n_bytes = (uint64_t)NERF_GRID_N_CELLS * (t->tb.max_cascade() + 1) * 4; }
-    else if (which == 1) { *ptr = (void*)t->tb.density_grid_bitfield(); *n_bytes = (uint64_t)NERF_GRID_N_CELLS * NERF_CASCADES / 8; }
+    if (which == 0) { *ptr = (void*)TB(t).density_grid(); *n_bytes = (uint64_t)NERF_GRID_N_CELLS * (TB(t).max_cascade() + 1) * 4; }
+    else if (which == 1) { *ptr = (void*)TB(t).density_grid_bitfield(); *n_bytes = (uint64_t)NERF_GRID_N_CELLS * NERF_CASCADES / 8; }
     else throw Error("density_grid: which must be 0 or 1");
     NGP_API_END
 }
 int ngp_testbed_render(ngp_testbed_t t, void* stream, const float* cam, const float* focal, const float* center, int32_t w, int32_t h, int32_t spp,
                        int32_t y0, int32_t y1, float* out, int32_t out_is_device, float* depth) {
     NGP_API_BEGIN require_device(); NGP_CHECK(t && cam && focal && center && out, "null argument");
-    t->tb.render(S(stream), cam, focal, center, w, h, spp, y0, y1, out, out_is_device != 0, depth);
+    TB(t).render(S(stream), cam, focal, center, w, h, spp, y0, y1, out, out_is_device != 0, depth);
     NGP_API_END
 }
 int ngp_testbed_render_frame(ngp_testbed_t t, void* stream, int32_t w, int32_t h, int32_t spp, int32_t linear, int32_t y0, int32_t y1, void* out, int32_t out_is_device) {
     NGP_API_BEGIN require_device(); NGP_CHECK(t && out, "null argument");
-    t->tb.render_frame(S(stream), w, h, spp, linear == 0, y0, y1, reinterpret_cast<float*>(out), out_is_device != 0);
+    TB(t).render_frame(S(stream), w, h, spp, linear == 0, y0, y1, reinterpret_cast<float*>(out), out_is_device != 0);
     NGP_API_END
 }
-int ngp_testbed_reset_camera(ngp_testbed_t t) { NGP_API_BEGIN NGP_CHECK(t, "null argument"); t->tb.reset_camera(); NGP_API_END }
-int ngp_testbed_set_nerf_camera_matrix(ngp_testbed_t t, const float* m) { NGP_API_BEGIN NGP_CHECK(t && m, "null argument"); t->tb.set_nerf_camera_matrix(m); NGP_API_END }
-int ngp_testbed_set_camera_to_training_view(ngp_testbed_t t, int32_t v) { NGP_API_BEGIN NGP_CHECK(t, "null argument"); t->tb.set_camera_to_training_view(v); NGP_API_END }
+int ngp_testbed_reset_camera(ngp_testbed_t t) { NGP_API_BEGIN NGP_CHECK(t, "null argument"); TB(t).reset_camera(); NGP_API_END }
+int ngp_testbed_set_nerf_camera_matrix(ngp_testbed_t t, const float* m) { NGP_API_BEGIN NGP_CHECK(t && m, "null argument"); TB(t).set_nerf_camera_matrix(m); NGP_API_END }
+int ngp_testbed_set_camera_to_training_view(ngp_testbed_t t, int32_t v) { NGP_API_BEGIN NGP_CHECK(t, "null argument"); TB(t).set_camera_to_training_view(v); NGP_API_END }
 namespace {
 float* vector_field(ngp::Testbed& tb, const std::string& n, uint32_t count) {
     struct E { const char* name; float* p; uint32_t n; };
@@ -523,42 +531,42 @@ int ngp_testbed_set_vector(ngp_testbed_t t, const char* name, const float* v, ui
 }
 int ngp_testbed_get_vector(ngp_testbed_t t, const char* name, float* v, uint32_t count) {
     NGP_API_BEGIN NGP_CHECK(t && name && v, "null argument");
-    if (std::string(name) == "dataset_offset") { NGP_CHECK(count == 3, "vector option 'dataset_offset' has 3 components"); memcpy(v, t->tb.dataset_offset(), 12); return 0; }   // read-only
+    if (std::string(name) == "dataset_offset") { NGP_CHECK(count == 3, "vector option 'dataset_offset' has 3 components"); memcpy(v, TB(t).dataset_offset(), 12); return 0; }   // read-only
     memcpy(v, vector_field(t->tb, name, count), count * sizeof(float));
     NGP_API_END
 }
 int ngp_testbed_set_render_lens(ngp_testbed_t t, int32_t lens_mode, const float* p) {
     NGP_API_BEGIN NGP_CHECK(t, "null argument");
     NGP_CHECK(lens_mode == LENS_PERSPECTIVE || (lens_mode == LENS_OPENCV && p), "render lens must be Perspective (0) or OpenCV (1) with 4 parameters");
-    t->tb.render_lens_mode = lens_mode;
-    for (int k = 0; k < 4; ++k) t->tb.render_lens_params[k] = (lens_mode == LENS_OPENCV) ? p[k] : 0.f;
+    TB(t).render_lens_mode = lens_mode;
+    for (int k = 0; k < 4; ++k) TB(t).render_lens_params[k] = (lens_mode == LENS_OPENCV) ? p[k] : 0.f;
     NGP_API_END
 }
-uint32_t ngp_testbed_n_training_views(ngp_testbed_t t) { return t ? (uint32_t)t->tb.training_views().size() : 0; }
+uint32_t ngp_testbed_n_training_views(ngp_testbed_t t) { return t ? (uint32_t)TB(t).training_views().size() : 0; }
 int ngp_testbed_training_view(ngp_testbed_t t, uint32_t i, ngp_training_image* o) {
-    NGP_API_BEGIN NGP_CHECK(t && o, "null argument"); NGP_CHECK(i < t->tb.training_views().size(), "Invalid frame index");
-    const ImageMeta& m = t->tb.training_views()[i];
+    NGP_API_BEGIN NGP_CHECK(t && o, "null argument"); NGP_CHECK(i < TB(t).training_views().size(), "Invalid frame index");
+    const ImageMeta& m = TB(t).training_views()[i];
     o->pixels = m.pixels; o->data_type = m.data_type; o->res[0] = m.res[0]; o->res[1] = m.res[1];
     memcpy(o->focal_length, m.focal_length, 8); memcpy(o->principal_point, m.principal_point, 8);
     o->lens_mode = m.lens_mode; memcpy(o->lens_params, m.lens_params, 16); memcpy(o->xform, m.xform, 48);
     NGP_API_END
 }
 int ngp_testbed_training_view_motion(ngp_testbed_t t, uint32_t i, float* xform_start12, float* xform_end12, float* rolling_shutter4) {
-    NGP_API_BEGIN NGP_CHECK(t, "null argument"); NGP_CHECK(i < t->tb.training_views().size() && t->tb.given_xform(i), "Invalid frame index");
-    if (xform_start12) memcpy(xform_start12, t->tb.given_xform(i), 48);
-    if (xform_end12) memcpy(xform_end12, t->tb.given_xform(i) + 12, 48);
-    if (rolling_shutter4) memcpy(rolling_shutter4, t->tb.training_views()[i].rolling_shutter, 16);
+    NGP_API_BEGIN NGP_CHECK(t, "null argument"); NGP_CHECK(i < TB(t).training_views().size() && TB(t).given_xform(i), "Invalid frame index");
+    if (xform_start12) memcpy(xform_start12, TB(t).given_xform(i), 48);
+    if (xform_end12) memcpy(xform_end12, TB(t).given_xform(i) + 12, 48);
+    if (rolling_shutter4) memcpy(rolling_shutter4, TB(t).training_views()[i].rolling_shutter, 16);
     NGP_API_END
 }
 int ngp_testbed_compute_image_mse(ngp_testbed_t t, void* stream, int32_t quantize, float* out) {
     NGP_API_BEGIN require_device(); NGP_CHECK(t && out, "null argument");
-    *out = t->tb.compute_image_mse(S(stream), quantize != 0);
+    *out = TB(t).compute_image_mse(S(stream), quantize != 0);
     NGP_API_END
 }
 
 int ngp_testbed_debug_buffer(ngp_testbed_t t, const char* name, void** ptr, uint64_t* n_bytes) {
     NGP_API_BEGIN NGP_CHECK(t && name && ptr && n_bytes, "null argument");
-    t->tb.debug_buffer(name, ptr, n_bytes);
+    TB(t).debug_buffer(name, ptr, n_bytes);
     NGP_API_END
 }
 
@@ -569,43 +577,45 @@ int ngp_testbed_debug_buffer(ngp_testbed_t t, const char* name, void** ptr, uint
     X(image_snap_to_pixel_centers, bool) X(image_linear_colors, bool) X(image_random_mode, int) X(sampler_lanes_per_ray, uint32_t) X(prefetch_rays, bool) X(prefetch_hits, uint32_t) X(dp_sharded_optimizer, bool) X(device_control_law, bool) \
     X(exposure, float) X(zoom, float) X(scale, float) X(ground_truth_alpha, float) X(render_near_distance, float) X(fov_axis, int) X(training_view, int)                      \
     X(color_space, int) X(tonemap_curve, int) X(render_mode, int) X(render_ground_truth, bool) X(render_with_lens_distortion, bool) X(render_row_stride, int) X(walk_ahead, bool) X(walk_ahead_hits, uint32_t) X(walk_ahead_misses, uint32_t) \
-    X(optimize_exposure, bool) X(exposure_l2_reg, float) X(n_steps_between_cam_updates, uint32_t) X(max_level_rand_training, bool) X(depth_supervision_lambda, float) X(depth_loss_type, int) X(optimize_extrinsics, bool) X(optimize_distortion, bool) X(extrinsic_l2_reg, float) X(extrinsic_learning_rate, float) \
+    X(optimize_exposure, bool) X(exposure_l2_reg, float) X(n_steps_between_cam_updates, uint32_t) X(max_level_rand_training, bool) X(depth_supervision_lambda, float) X(depth_loss_type, int) X(deferred_step_finish, bool) X(optimize_extrinsics, bool) X(optimize_distortion, bool) X(extrinsic_l2_reg, float) X(extrinsic_learning_rate, float) \
     X(sample_focal_plane_proportional_to_error, bool) X(sample_image_proportional_to_error, bool) X(n_steps_between_error_map_updates, uint32_t)
 
 int ngp_testbed_set_option(ngp_testbed_t t, const char* name, double value) {
     NGP_API_BEGIN NGP_CHECK(t && name, "null argument");
     const std::string n = name;
-#define X(field, type) if (n == #field) { t->tb.field = (type)value; return 0; }
+#define X(field, type) if (n == #field) { TB(t).field = (type)value; return 0; }
     NGP_OPTIONS(X)
 #undef X
-    if (n == "background_r") { t->tb.background_color[0] = (float)value; return 0; }
-    if (n == "background_g") { t->tb.background_color[1] = (float)value; return 0; }
-    if (n == "background_b") { t->tb.background_color[2] = (float)value; return 0; }
-    if (n == "background_a") { t->tb.background_color[3] = (float)value; return 0; }
-    if (n == "fov") { t->tb.set_fov((float)value); return 0; }
-    if (n == "image_stratified") { t->tb.image_random_mode = value != 0 ? IMG_RANDOM_STRATIFIED : IMG_RANDOM_RANDOM; return 0; }   // round-1 name
+    if (n == "background_r") { TB(t).background_color[0] = (float)value; return 0; }
+    if (n == "background_g") { TB(t).background_color[1] = (float)value; return 0; }
+    if (n == "background_b") { TB(t).background_color[2] = (float)value; return 0; }
+    if (n == "background_a") { TB(t).background_color[3] = (float)value; return 0; }
+    if (n == "fov") { TB(t).set_fov((float)value); return 0; }
+    if (n == "image_stratified") { TB(t).image_random_mode = value != 0 ? IMG_RANDOM_STRATIFIED : IMG_RANDOM_RANDOM; return 0; }   // round-1 name
     throw Error("unknown option '" + n + "'");
     NGP_API_END
 }
 int ngp_testbed_get_option(ngp_testbed_t t, const char* name, double* value) {
     NGP_API_BEGIN NGP_CHECK(t && name && value, "null argument");
     const std::string n = name;
-#define X(field, type) if (n == #field) { *value = (double)t->tb.field; return 0; }
+#define X(field, type) if (n == #field) { *value = (double)TB(t).field; return 0; }
     NGP_OPTIONS(X)
 #undef X
-    if (n == "background_r") { *value = t->tb.background_color[0]; return 0; }
-    if (n == "background_g") { *value = t->tb.background_color[1]; return 0; }
-    if (n == "background_b") { *value = t->tb.background_color[2]; return 0; }
-    if (n == "background_a") { *value = t->tb.background_color[3]; return 0; }
-    if (n == "fov") { *value = t->tb.fov(); return 0; }
-    if (n == "image_stratified") { *value = t->tb.image_random_mode == IMG_RANDOM_STRATIFIED; return 0; }
-    if (n == "error_map_width") { *value = t->tb.error_map_res()[0]; return 0; }            // read-only: the lattice of the current error-map window
-    if (n == "error_map_height") { *value = t->tb.error_map_res()[1]; return 0; }
-    if (n == "error_cdf_width") { *value = t->tb.error_cdf_res()[0]; return 0; }            // ... and of the CDFs in use (0: none yet)
-    if (n == "error_cdf_height") { *value = t->tb.error_cdf_res()[1]; return 0; }
-    if (n == "dataset_scale") { *value = t->tb.dataset_scale(); return 0; }              // read-only: nerf.training.dataset.scale / aabb_scale
-    if (n == "dataset_aabb_scale") { *value = t->tb.dataset_aabb_scale(); return 0; }
-    if (n == "l2_window_bytes") { *value = t->tb.trainer() ? (double)t->tb.trainer()->l2_window_bytes : 0.0; return 0; }   // read-only
+    if (n == "background_r") { *value = TB(t).background_color[0]; return 0; }
+    if (n == "background_g") { *value = TB(t).background_color[1]; return 0; }
+    if (n == "background_b") { *value = TB(t).background_color[2]; return 0; }
+    if (n == "background_a") { *value = TB(t).background_color[3]; return 0; }
+    if (n == "fov") { *value = TB(t).fov(); return 0; }
+    if (n == "image_stratified") { *value = TB(t).image_random_mode == IMG_RANDOM_STRATIFIED; return 0; }
+    if (n == "error_map_width") { *value = TB(t).error_map_res()[0]; return 0; }            // read-only: the lattice of the current error-map window
+    if (n == "error_map_height") { *value = TB(t).error_map_res()[1]; return 0; }
+    if (n == "error_cdf_width") { *value = TB(t).error_cdf_res()[0]; return 0; }            // ... and of the CDFs in use (0: none yet)
+    if (n == "error_cdf_height") { *value = TB(t).error_cdf_res()[1]; return 0; }
+    if (n == "dataset_scale") { *value = TB(t).dataset_scale(); return 0; }              // read-only: nerf.training.dataset.scale / aabb_scale
+    if (n == "dataset_aabb_scale") { *value = TB(t).dataset_aabb_scale(); return 0; }
+    if (n == "measured_batch_size_total") { *value = (double)TB(t).measured_total(); return 0; }                          // read-only: sums over all steps so far
+    if (n == "measured_batch_size_before_compaction_total") { *value = (double)TB(t).measured_before_total(); return 0; }
+    if (n == "l2_window_bytes") { *value = TB(t).trainer() ? (double)TB(t).trainer()->l2_window_bytes : 0.0; return 0; }   // read-only
     throw Error("unknown option '" + n + "'");
     NGP_API_END
 }

@@ -7,6 +7,9 @@
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#if defined(__SSE2__)
+#include <emmintrin.h>
+#endif
 
 namespace ngp {
 
@@ -25,14 +28,36 @@ static int loss_type_from_string(const std::string& s) {   // string_to_loss_typ
 }
 
 // RGBA8 pixels equal to 0x00FF00FF are "masked away" (read_rgba, common_device.cuh:885-913): the training walk skips rays that
-// land on them, i.e. the walk depends on the image CONTENT only through this one value.  One pass over the host buffer
-// (auto-vectorised OR-reduction, ~0.1 ms for an 800x800 view) tells whether a view has any.
+// land on them, i.e. the walk depends on the image CONTENT only through this one value, and set_training_image needs to know — on the
+// host and at once, before the next step may adopt a prefetched walk — whether a new view has any.  The scan reads the 2.56 MB of an
+// 800x800 view from DRAM; as one linear stream that took 0.25-0.27 ms on the B200 box's host and made the upload path of bench.py
+// HOST-bound (0.573 ms per step against 0.527 with the scan skipped).  Eight interleaved streams, a cache line each per iteration, keep
+// more misses in flight: 0.15 ms (tools/scratch/scan_bench.cpp, profiles/r02_host_scan.txt).  A pool of sleeping worker threads was
+// measured too: 0.07 ms in a tight loop, but with 0.5 ms between calls the wake-ups cost more than the scan (e2e 462 -> 325 M samples/s).
 static bool has_mask_pixels(const void* pixels, size_t n_pixels) {
     const uint32_t* p = static_cast<const uint32_t*>(pixels);
     uint32_t any = 0;
-    for (size_t i = 0; i < n_pixels; ++i) any |= (uint32_t)(p[i] == 0x00FF00FFu);
+    size_t done = 0;
+#if defined(__SSE2__)
+    constexpr size_t S = 8;
+    const size_t c = (n_pixels / S) & ~(size_t)15;     // pixels per stream, whole cache lines
+    __m128i acc = _mm_setzero_si128();
+    const __m128i key = _mm_set1_epi32(0x00FF00FF);
+    for (size_t i = 0; i < c; i += 16) {
+        for (size_t s = 0; s < S; ++s) {
+            const __m128i* q = reinterpret_cast<const __m128i*>(p + s * c + i);
+            acc = _mm_or_si128(acc, _mm_cmpeq_epi32(_mm_loadu_si128(q), key)); acc = _mm_or_si128(acc, _mm_cmpeq_epi32(_mm_loadu_si128(q + 1), key));
+            acc = _mm_or_si128(acc, _mm_cmpeq_epi32(_mm_loadu_si128(q + 2), key)); acc = _mm_or_si128(acc, _mm_cmpeq_epi32(_mm_loadu_si128(q + 3), key));
+        }
+    }
+    any = _mm_movemask_epi8(acc) != 0;
+    done = c * S;
+#endif
+    for (size_t i = done; i < n_pixels; ++i) any |= (uint32_t)(p[i] == 0x00FF00FFu);
     return any != 0;
 }
+
+bool host_has_mask_pixels(const void* rgba8_pixels, size_t n_pixels) { return has_mask_pixels(rgba8_pixels, n_pixels); }
 
 Testbed::Testbed(int mode) : m_mode(mode), m_rng(1337), m_density_grid_rng(1337) {
     NGP_CHECK(mode == MODE_TB_NERF || mode == MODE_TB_IMAGE || mode == MODE_TB_SDF, "Testbed: unknown mode (Nerf = 0, Sdf = 1, Image = 2)");
@@ -501,7 +526,8 @@ void Testbed::set_training_image(cudaStream_t s, uint32_t frame_idx, const void*
     // on the content and stays valid; otherwise (and for float images, where any negative value masks) it is discarded.
     bool content_matters = !m_all_images_u8;
     if (m_all_images_u8) {
-        const bool new_mask = has_mask_pixels(pixels_host, m_image_bytes[frame_idx] / 4);
+        static const bool skip_scan = getenv("NGP_DEBUG_SKIP_MASK_SCAN") != nullptr;   // measurement only: what the host-side scan costs the upload path
+        const bool new_mask = skip_scan ? false : has_mask_pixels(pixels_host, m_image_bytes[frame_idx] / 4);
         content_matters = new_mask || m_frame_has_mask[frame_idx];
         m_frame_has_mask[frame_idx] = new_mask;
     }
@@ -584,6 +610,7 @@ void Testbed::training_prep_nerf(cudaStream_t s) {
 void Testbed::train(cudaStream_t s, uint32_t batch_size) { train_begin(s, batch_size); train_end(s, 0, 0); }
 
 void Testbed::train_begin(cudaStream_t s, uint32_t batch_size) {
+    finish_pending_step();
     if (!m_trainer) reload_network_from_file();          // testbed.cu:4297-4306: training data without an explicitly loaded network -> the default config
     NGP_CHECK(m_trainer, "Unable to create a neural network trainer.");
     NGP_CHECK(batch_size >= BATCH_GRANULARITY && batch_size % BATCH_GRANULARITY == 0, "training batch size must be a multiple of 256");
@@ -656,6 +683,23 @@ void Testbed::train_end(cudaStream_t s, uint32_t measured_override, uint32_t mea
         if (m_get_loss) { NGP_CUDA_CHECK(cudaMemcpyAsync(&m_loss_scalar, m_loss_sum.as<float>(), 4, cudaMemcpyDeviceToHost, s)); NGP_CUDA_CHECK(cudaStreamSynchronize(s)); }
         return;
     }
+    // the host half may wait: the next sampler is already in flight behind the device-side law, and nothing else here touches the device
+    static const bool defer_env = [] { const char* e = getenv("NGP_DEFER_FINISH"); return e ? atoi(e) != 0 : true; }();
+    if (deferred_step_finish && defer_env && m_early_prefetch && !m_get_loss && !m_comm && !measured_override && !measured_before_override && !walk_ahead &&
+        !optimize_exposure && !m_error_map_live) {
+        m_finish_pending = true; m_finish_target = target; m_finish_stream = s;
+        return;
+    }
+    finish_step(s, target, measured_override, measured_before_override);
+}
+
+void Testbed::finish_pending_step() {
+    if (!m_finish_pending) return;
+    m_finish_pending = false;
+    finish_step(m_finish_stream, m_finish_target, 0, 0);
+}
+
+void Testbed::finish_step(cudaStream_t s, uint32_t target, uint32_t measured_override, uint32_t measured_before_override) {
     // NerfCounters::update_after_training (testbed_nerf.cu:3583-3609): two counters (+ the loss every 16 steps) read back.
     // The counters were copied to pinned memory right after the loss kernel (train_nerf_step), so the host has them while
     // the backward pass and the optimizer are still running: time enough to start the next step's rays beside them.
@@ -678,6 +722,7 @@ void Testbed::train_end(cudaStream_t s, uint32_t measured_override, uint32_t mea
         cudaStreamSynchronize(s);
         throw Error("Nerf training generated 0 samples. Aborting training.");   // testbed_nerf.cu:3693-3697
     }
+    m_measured_total += m_measured; m_measured_before_total += m_measured_before;
     m_rays_per_batch = (uint32_t)((float)m_rays_per_batch * (float)target / (float)m_measured);
     m_rays_per_batch = std::min((uint32_t)next_multiple(m_rays_per_batch, BATCH_GRANULARITY), 1u << 18);
     // camera-side optimisers (testbed_nerf.cu:3754-3861; of those this library trains the exposure)

@@ -25,6 +25,7 @@ struct TrainStats {
     float learning_rate; float density_grid_mean;
 };
 
+bool host_has_mask_pixels(const void* rgba8_pixels, size_t n_pixels);   // MaskScanPool (testbed.cu)
 class Testbed {
 public:
     explicit Testbed(int mode);
@@ -100,6 +101,14 @@ public:
     void train(cudaStream_t s, uint32_t batch_size);
     void train_begin(cudaStream_t s, uint32_t batch_size);
     void train_end(cudaStream_t s, uint32_t measured_override, uint32_t measured_before_override);
+    // The host half of a NeRF step's end (NerfCounters::update_after_training: wait for the two counters, control law, next prefetch).  When the
+    // next step's sampler is already in flight behind the device-side control law, nothing on the device waits for it, so train_end leaves it
+    // pending and the host returns to the caller at once; it runs at the start of the next step or when anything else looks at the testbed
+    // (every C-ABI entry point except set_training_image calls finish_pending_step first).  deferred_step_finish = false: always in train_end.
+    void finish_pending_step();
+    bool deferred_step_finish = true;
+    uint64_t measured_total() const { return m_measured_total; }                  // sums of the per-step counts since the testbed was made
+    uint64_t measured_before_total() const { return m_measured_before_total; }
     void set_shard(uint32_t rank, uint32_t world) { m_rank = rank; m_world = world; }
     // local sample counts of the step begun by train_begin, available as soon as its loss kernel has run (the backward pass is
     // still in flight): lets a data-parallel host exchange them while the device works
@@ -226,6 +235,9 @@ private:
 
     // NeRF dataset + occupancy grid
     float m_density_grid_mean = 0.f;      // host copy, refreshed with the loss every 16th step
+    void finish_step(cudaStream_t s, uint32_t target, uint32_t measured_override, uint32_t measured_before_override);
+    bool m_finish_pending = false; uint32_t m_finish_target = 0; cudaStream_t m_finish_stream = nullptr;
+    uint64_t m_measured_total = 0, m_measured_before_total = 0;
     std::vector<bool> m_frame_has_mask;   // RGBA8 view contains the mask colour 0x00FF00FF (see set_training_image)
     uint32_t m_n_images = 0; int m_aabb_scale = 1; uint32_t m_max_cascade = 0;
     std::vector<float*> m_depth_buffers;                    // per view: device depth map (NerfDataset::depthmemory) or nullptr

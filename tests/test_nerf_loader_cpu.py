@@ -246,3 +246,28 @@ def test_depth_paths(L, tmp_path):
         L.check(lib.ngp_nerf_dataset_set_depth(d, 0, good.ctypes.data_as(C.c_void_p), 8, 6))
     finally:
         lib.ngp_nerf_dataset_close(d)
+
+
+def test_host_mask_scan(L):
+    """The test set_training_image applies to an RGBA8 view on the host (mask colour 0x00FF00FF of read_rgba, common_device.cuh:885-913): the
+    eight-stream scan finds a single masked pixel wherever it sits (stream borders and the scalar tail included), at small and odd sizes too."""
+    lib = L.lib()
+
+    def has(px):
+        out = C.c_int32(-1)
+        L.check(lib.ngp_host_has_mask_pixels(px.ctypes.data_as(C.c_void_p), px.size, C.byref(out)))
+        return out.value
+
+    rng = np.random.default_rng(11)
+    for n in (0, 1, 7, 1000, (1 << 17) - 1, 1 << 17, 800 * 800, 800 * 800 + 3):
+        px = rng.integers(0, 1 << 32, size=max(n, 1), dtype=np.uint32)[:n]
+        px[px == 0x00FF00FF] = 0
+        assert has(px) == 0
+        if n == 0:
+            continue
+        parts = [0, n - 1, n // 2] + [min(n - 1, max(0, (n + k - 1) // k * j + d)) for k in range(2, 9) for j in range(1, k) for d in (-1, 0)]
+        for i in parts:
+            q = px.copy(); q[i] = 0x00FF00FF
+            assert has(q) == 1, (n, i)
+        near = px.copy(); near[n // 3] = 0x01FF00FF                  # alpha 1: not the mask colour
+        assert has(near) == 0
