@@ -685,7 +685,7 @@ void Testbed::train_end(cudaStream_t s, uint32_t measured_override, uint32_t mea
     }
     // the host half may wait: the next sampler is already in flight behind the device-side law, and nothing else here touches the device
     static const bool defer_env = [] { const char* e = getenv("NGP_DEFER_FINISH"); return e ? atoi(e) != 0 : true; }();
-    if (deferred_step_finish && defer_env && m_early_prefetch && !m_get_loss && !m_comm && !measured_override && !measured_before_override && !walk_ahead &&
+    if (deferred_step_finish && defer_env && m_early_prefetch && !m_comm && !measured_override && !measured_before_override && !walk_ahead &&
         !optimize_exposure && !m_error_map_live) {
         m_finish_pending = true; m_finish_target = target; m_finish_stream = s;
         return;
@@ -703,11 +703,7 @@ void Testbed::finish_step(cudaStream_t s, uint32_t target, uint32_t measured_ove
     // NerfCounters::update_after_training (testbed_nerf.cu:3583-3609): two counters (+ the loss every 16 steps) read back.
     // The counters were copied to pinned memory right after the loss kernel (train_nerf_step), so the host has them while
     // the backward pass and the optimizer are still running: time enough to start the next step's rays beside them.
-    if (m_get_loss) {
-        reduce_sum_f32(s, m_loss.as<float>(), m_rays_per_batch, m_loss_sum.as<float>(), m_partials.as<float>());
-        NGP_CUDA_CHECK(cudaMemcpyAsync(m_host_counters + 4, m_loss_sum.as<float>(), 4, cudaMemcpyDeviceToHost, s));
-        NGP_CUDA_CHECK(cudaMemcpyAsync(m_host_counters + 7, m_mean.as<float>(), 4, cudaMemcpyDeviceToHost, s));   // stats().density_grid_mean
-    }
+    // (the loss sum of every 16th step was reduced and copied right behind the loss kernel, train_nerf_step: it arrives with the counters)
     NGP_CUDA_CHECK(cudaEventSynchronize(m_ev_counters));
     const uint32_t* c = m_host_counters;
     if (m_comm && !measured_override && !measured_before_override) {   // lock-step control law: the mean counts over the ranks
@@ -760,9 +756,8 @@ void Testbed::finish_step(cudaStream_t s, uint32_t target, uint32_t measured_ove
     launch_walk_ahead(target);
     // No host wait for the optimizer: the control law only needed the counters (already here), and everything that consumes
     // the new weights is ordered behind them on `s`.  The host so runs half a step ahead and the device never idles between
-    // steps.  Only the loss read-back (every 16th step) has to wait for its reduction.
+    // steps.  The loss of every 16th step came with the counters.
     if (m_get_loss) {
-        NGP_CUDA_CHECK(cudaStreamSynchronize(s));
         float loss_sum; memcpy(&loss_sum, m_host_counters + 4, 4); m_loss_scalar = loss_sum * (float)m_measured / (float)target;
         // data parallel: every ray's loss is divided by the GLOBAL ray count but only this rank's rays are summed here, so the sum is
         // ~1/world of the step's loss; scaled back it is this rank's estimate of the global mean (comparable with single-GPU runs)
@@ -1030,6 +1025,11 @@ void Testbed::train_nerf_step(cudaStream_t s, uint32_t target) {
     if (m_copy_pending) { NGP_CUDA_CHECK(cudaStreamWaitEvent(s, m_ev_copy_done, 0)); m_copy_pending = false; }   // uploaded view(s), see set_training_image
     nerf_compute_loss(s, R, aabb, n_rays_total, m_rng, target, lc, m_n_images, m_metas.as<ImageMeta>(), m_mean.as<float>(), ray_offset, n_rays_global, sb, lb);
     NGP_CUDA_CHECK(cudaMemcpyAsync(m_host_counters, sb.counters, 16, cudaMemcpyDeviceToHost, s));   // read by train_end
+    if (m_get_loss) {   // every 16th step (testbed.cu:4349-4353): the per-ray losses are final here, so the sum travels with the counters and nothing waits for the optimizer
+        reduce_sum_f32(s, m_loss.as<float>(), R, m_loss_sum.as<float>(), m_partials.as<float>());
+        NGP_CUDA_CHECK(cudaMemcpyAsync(m_host_counters + 4, m_loss_sum.as<float>(), 4, cudaMemcpyDeviceToHost, s));
+        NGP_CUDA_CHECK(cudaMemcpyAsync(m_host_counters + 7, m_mean.as<float>(), 4, cudaMemcpyDeviceToHost, s));   // stats().density_grid_mean
+    }
     NGP_CUDA_CHECK(cudaEventRecord(m_ev_counters, s));
     // device-side control law for the next step's sampler (single rank; data parallel keeps the host path: the law sees the rank mean)
     uint32_t early_rays_bound = 0, early_samples_bound = 0;

@@ -10,5 +10,5 @@ print('value', round(b['value']/1e6,1), 'ms', round(b['ms_per_step'],4), 'e2e', 
 " ) >> gpurun_out/e2e_ab.txt
 done
 ( timeout 300 python tools/host_time.py 2>&1 | tail -8 ) >> gpurun_out/e2e_ab.txt
-( timeout 600 python -m pytest tests/test_nerf_gpu.py tests/test_prefetch_gpu.py -x -q -m gpu 2>&1 | tail -3 ) >> gpurun_out/e2e_ab.txt
+( timeout 600 python -m pytest tests/test_nerf_gpu.py tests/test_exposure_gpu.py tests/test_snapshot_gpu.py -x -q -m gpu 2>&1 | tail -3 ) >> gpurun_out/e2e_ab.txt
 cat gpurun_out/e2e_ab.txt
