@@ -598,6 +598,7 @@ int ngp_testbed_set_option(ngp_testbed_t t, const char* name, double value) {
 int ngp_testbed_get_option(ngp_testbed_t t, const char* name, double* value) {
     NGP_API_BEGIN NGP_CHECK(t && name && value, "null argument");
     const std::string n = name;
+    if (n == "training_step") { *value = (double)t->tb.training_step(); return 0; }   // read-only; does not wait for a pending step's counters (run.py:183-202 polls it every frame)
 #define X(field, type) if (n == #field) { *value = (double)TB(t).field; return 0; }
     NGP_OPTIONS(X)
 #undef X

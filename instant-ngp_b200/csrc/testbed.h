@@ -107,6 +107,7 @@ public:
     // (every C-ABI entry point except set_training_image calls finish_pending_step first).  deferred_step_finish = false: always in train_end.
     void finish_pending_step();
     bool deferred_step_finish = true;
+    uint32_t training_step() const { return m_training_step; }                     // host counter: valid while a step's host half is pending
     uint64_t measured_total() const { return m_measured_total; }                  // sums of the per-step counts since the testbed was made
     uint64_t measured_before_total() const { return m_measured_before_total; }
     void set_shard(uint32_t rank, uint32_t world) { m_rank = rank; m_world = world; }

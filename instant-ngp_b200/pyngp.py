@@ -173,7 +173,7 @@ def _stream():
 
 
 _BOOL_OPTS = {"random_bg_color", "linear_colors", "snap_to_pixel_centers", "train_snap_to_pixel_centers", "shall_train_encoding", "shall_train_network",
-              "image_snap_to_pixel_centers", "image_linear_colors", "image_stratified", "prefetch_rays", "dp_sharded_optimizer", "device_control_law",
+              "image_snap_to_pixel_centers", "image_linear_colors", "image_stratified", "prefetch_rays", "dp_sharded_optimizer", "device_control_law", "deferred_step_finish",
               "render_ground_truth", "render_with_lens_distortion", "walk_ahead", "optimize_exposure", "max_level_rand_training", "optimize_extrinsics", "optimize_distortion",
               "sample_focal_plane_proportional_to_error", "sample_image_proportional_to_error"}
 _FLOAT_OPTS = {"near_distance", "density_grid_decay", "render_min_transmittance", "cone_angle_constant", "exposure", "zoom", "fov", "ground_truth_alpha",
@@ -912,7 +912,7 @@ class Testbed:
 
     @property
     def training_step(self):
-        return self.stats.training_step
+        return int(self.get_option("training_step"))      # the host's step counter: no wait for the step in flight (stats / loss do wait)
 
     @property
     def loss(self):

@@ -359,6 +359,33 @@ def test_device_control_law_trains_identically(env):
     assert runs[0][1] > 20 and runs[1][1] > 20, (runs[0][1], runs[1][1])
 
 
+def test_deferred_step_finish_trains_identically(env):
+    """deferred_step_finish (default on): when the next step's sampler already runs behind the device-side law, train() returns without
+    waiting for the step's counters and the host half of the step's end (NerfCounters::update_after_training, testbed_nerf.cu:3583-3609) runs at
+    the start of the next call.  Same arithmetic at a later moment: per-step traces, the running sums and the losses of every 16th step are
+    identical with it off, with and without a view uploaded between the steps; training_step is current without forcing the wait."""
+    runs = []
+    for deferred in (True, False):
+        tb = _testbed(env)
+        tb.deferred_step_finish = deferred
+        trace, losses = [], []
+        for i in range(70):
+            if i >= 30:
+                tb.set_training_image(i % N_VIEWS, env["views"][i % N_VIEWS]["pixels"])      # the same pixels again: content unchanged
+            tb.train(BATCH)
+            assert tb.training_step == i + 1
+            if i % 3 == 0 or i >= 60:                                                         # most steps are left pending on purpose
+                st = tb.stats
+                trace.append((i, st.rays_per_batch, st.measured_batch_size, st.measured_batch_size_before_compaction))
+                losses.append(st.loss)
+        totals = (tb.get_option("measured_batch_size_total"), tb.get_option("measured_batch_size_before_compaction_total"))
+        runs.append((trace, totals, losses, int(tb.prefetch_hits)))
+    assert runs[0][0] == runs[1][0] and runs[0][1] == runs[1][1]
+    assert runs[0][3] > 20 and runs[0][3] == runs[1][3]
+    np.testing.assert_allclose(runs[0][2], runs[1][2], rtol=2e-2)          # float atomics in the steps before: equal up to their order
+    assert runs[0][1][0] > 60 * BATCH * 0.5 and all(np.isfinite(runs[0][2]))
+
+
 def test_native_data_parallel_step_world_size_1(env):
     """the in-library data-parallel step (NCCL communicator bound at run time, counters + gradient all-reduce on the
     communication stream) with a single rank must train exactly like the plain step"""
