@@ -32,7 +32,7 @@ static int loss_type_from_string(const std::string& s) {   // string_to_loss_typ
 // host and at once, before the next step may adopt a prefetched walk — whether a new view has any.  The scan reads the 2.56 MB of an
 // 800x800 view from DRAM; as one linear stream that took 0.25-0.27 ms on the B200 box's host and made the upload path of bench.py
 // HOST-bound (0.573 ms per step against 0.527 with the scan skipped).  Eight interleaved streams, a cache line each per iteration, keep
-// more misses in flight: 0.15 ms (tools/scratch/scan_bench.cpp, profiles/r02_host_scan.txt).  A pool of sleeping worker threads was
+// more misses in flight: 0.15 ms (tools/scan_bench.cpp, profiles/r02_host_scan.txt).  A pool of sleeping worker threads was
 // measured too: 0.07 ms in a tight loop, but with 0.5 ms between calls the wake-ups cost more than the scan (e2e 462 -> 325 M samples/s).
 static bool has_mask_pixels(const void* pixels, size_t n_pixels) {
     const uint32_t* p = static_cast<const uint32_t*>(pixels);
