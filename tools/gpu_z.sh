@@ -1,4 +1,4 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 1500 python -m pytest tests/test_nerf_gpu.py tests/test_run_script_gpu.py -x -q -m gpu -k "deferred or control_law or run_py or set_training_image" > gpurun_out/z_pytest.txt 2>&1
-tail -5 gpurun_out/z_pytest.txt
+( timeout 600 python -m pytest tests/test_psnr_parity_gpu.py -x -q -m gpu -s 2>&1 | grep "PSNR:\|passed\|failed\|Error" | cut -c1-140 ) > gpurun_out/z_pytest.txt 2>&1
+cat gpurun_out/z_pytest.txt
