@@ -347,7 +347,7 @@ def run_own(args):
     (ms_e2e, n_e2e, _, _), rows_e2e = windows(1 if ncu else max(3, args.repeats // 3), upload=True)
     view_bytes = int(views[0]["pixels"].numel())
     loss_steps = sum(1 for i in range(args.steps) if i % 16 == 0)
-    d2h = 16 + 4.0 * loss_steps / args.steps
+    d2h = 16 + 8.0 * loss_steps / args.steps       # two counters (+ two reserved words) every step; loss sum and density-grid mean every 16th
 
     # per-kernel CUDA-event timing on the launching stream over a separate pass of K steps (events add ~2 records per kernel,
     # so this pass is not the one `value` comes from)

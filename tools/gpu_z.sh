@@ -1,4 +1,4 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 160 python -m pytest $(ls tests/test_*.py | sort | awk '$0 > "tests/test_psnr_parity_gpu.py"') -x -q -m gpu > gpurun_out/z_pytest.txt 2>&1
-tail -4 gpurun_out/z_pytest.txt
+timeout 100 python bench.py --steps 20 --warmup 5 --no-cpu-baseline > gpurun_out/z_bench.json 2> gpurun_out/z_bench.err
+tail -c 300 gpurun_out/z_bench.json
