@@ -2,8 +2,8 @@
 import collections, re, subprocess, sys, os
 root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sass = subprocess.run(["cuobjdump", "-sass", os.path.join(root, "instant-ngp_b200", "libngp_b200.so")], capture_output=True, text=True).stdout
-WANT = ["UTCHMMA", "LDTM", "UBLKCP", "UTCBAR", "SYNCS", "REDG.E.ADD.F16x2", "REDG.E.ADD.F16x4", "REDG.E.ADD.F32x4", "REDG.E.ADD.F32", "RED.E.ADD.F16x2", "ATOMG", "LDG.E.64", "LDG.E.128", "STG.E.128"]
-HEAD = ["mlp_forward_kernelILj32ELj1ELj2ELi0E", "mlp_backward_kernelILj32ELj1ELj2ELi0ELb1", "grid_forward_kernelILj3ELj2E", "grid_backward_kernelILj3ELj2E", "adam_kernel",
+WANT = ["UTCHMMA", "LDTM", "STTM", "UBLKCP", "UTCBAR", "SYNCS", "REDG.E.ADD.F16x2", "REDG.E.ADD.F16x4", "REDG.E.ADD.F32x4", "REDG.E.ADD.F32", "RED.E.ADD.F16x2", "ATOMG", "LDG.E.64", "LDG.E.128", "STG.E.128"]
+HEAD = ["mlp_forward_ts_kernelILj32ELj1ELj2ELi0E", "mlp_forward_kernelILj32ELj1ELj2ELi0E", "mlp_backward_kernelILj32ELj1ELj2ELi0ELb1ELb0ELb0E", "mlp_backward_kernelILj32ELj1ELj2ELi0ELb1ELb1ELb0E", "grid_forward_kernelILj3ELj2E", "grid_backward_kernelILj3ELj2E", "adam_kernel",
         "sampler_count_group_kernelILj8ELb1ELj1E", "sampler_expand_kernel", "loss_forward_group_kernelILj32E", "loss_backward_group_kernelILj32E"]
 cur, counts, sample = None, collections.defaultdict(collections.Counter), {}
 for line in sass.splitlines():
